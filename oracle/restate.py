@@ -1,0 +1,403 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU restatement (the "oracle") of the caption-decoder hot path.
+
+Plain functional fp32 torch-on-CPU code over a flat ``state_dict`` (no nn.Module, no autograd
+tricks), one function per reference symbol, each citing the reference file:line it follows
+(paths relative to /root/reference).  `torch` is the arithmetic provider exactly as it is for the
+reference itself (every op on this path is in-tree Python over ATen).
+
+PINNING: the reference ships no tests / golden vectors for this path, so the
+oracle is pinned against the reference ITSELF: `tests/test_oracle_vs_reference.py` imports the
+unmodified reference modules in the build container (oracle/ref_import.py) and compares; and
+`oracle/make_golden.py` froze reference outputs into `tests/golden/*.pt`, which
+`tests/test_oracle_golden.py` checks on any machine.
+
+Only `tests/`, `__graft_entry__.smoke()` and `bench.py`'s cpu_baseline / `--impl reference` leg may
+import this module.  The product package never does.
+"""
+import math
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.nn.functional as F
+
+SD = Dict[str, torch.Tensor]
+
+
+# ----------------------------------------------------------------------------- linear pieces
+def fold_weight_norm(g: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
+    """w = g * v / ||v||_row  -- ttl/tell/modules/linear.py:30-33 (nn.utils.weight_norm, dim=0)."""
+    return v * (g / v.norm(dim=1, keepdim=True))
+
+
+def gehring_linear(x: torch.Tensor, sd: SD, p: str) -> torch.Tensor:
+    """GehringLinear forward -- ttl/tell/modules/linear.py:7-33."""
+    if p + 'weight_g' in sd:
+        w = fold_weight_norm(sd[p + 'weight_g'], sd[p + 'weight_v'])
+    else:
+        w = sd[p + 'weight']
+    return F.linear(x, w, sd.get(p + 'bias'))
+
+
+def layer_norm(x: torch.Tensor, sd: SD, p: str, eps: float = 1e-5) -> torch.Tensor:
+    """nn.LayerNorm(embed_dim) -- ttl/tell/models/decoder_flattened.py:245,254,259,268."""
+    mu = x.mean(-1, keepdim=True)
+    var = ((x - mu) ** 2).mean(-1, keepdim=True)
+    return (x - mu) / torch.sqrt(var + eps) * sd[p + 'weight'] + sd[p + 'bias']
+
+
+# ----------------------------------------------------------------------------- DynamicConv
+def dynconv_taps(x: torch.Tensor, w_tap: torch.Tensor, H: int, K: int) -> torch.Tensor:
+    """softmax over ALL K tap logits per (t, b, head) -- dynamic.py:300-304.  [T,B,H,K]"""
+    T, B, C = x.shape
+    return F.softmax(F.linear(x, w_tap).view(T, B, H, K), dim=-1)
+
+
+def dynamic_conv(x: torch.Tensor, w_tap: torch.Tensor, H: int, K: int) -> torch.Tensor:
+    """Causal DynamicConv1dTBC (padding_l = K-1, weight_softmax, no renorm, no bias).
+
+    y[t,b,h*R+r] = sum_j w[t,b,h,j] * x[t-(K-1)+j, b, h*R+r], x[<0] = 0; the taps that reach
+    before t=0 are DROPPED AFTER the softmax (not renormalised) -- ttl/tell/modules/convolutions/
+    dynamic.py:285-336 (band matrix + narrow(2, P, T)); same result as the unfold path :122-190.
+    """
+    T, B, C = x.shape
+    R = C // H
+    w = dynconv_taps(x, w_tap, H, K)                      # [T,B,H,K]
+    xp = F.pad(x, (0, 0, 0, 0, K - 1, 0))                 # left-pad time with K-1 zeros
+    win = xp.unfold(0, K, 1)                              # [T,B,C,K]; win[t,...,j] = x[t-(K-1)+j]
+    y = torch.einsum('tbhrk,tbhk->tbhr', win.reshape(T, B, H, R, K), w)
+    return y.reshape(T, B, C)
+
+
+def dynamic_conv_step(x_new: torch.Tensor, hist: Optional[torch.Tensor], w_tap: torch.Tensor,
+                      H: int, K: int):
+    """Incremental DynamicConv -- dynamic.py:95-99,114-116: keep the last K-1 conv inputs,
+    re-run the conv over [hist ; new] and keep only the new rows.  Returns (y_new, new_hist).
+    When the window is shorter than K the reference narrows the tap vector to its LAST `len`
+    entries (:324-326), which is what left zero padding computes."""
+    xs = x_new if hist is None else torch.cat([hist, x_new], 0)
+    y = dynamic_conv(xs, w_tap, H, K)
+    y = y if hist is None else y[hist.shape[0]:]
+    new_hist = xs[-(K - 1):] if K > 1 else xs[:0]
+    return y, new_hist
+
+
+# ----------------------------------------------------------------------------- attention
+def mha_params(sd: SD, p: str, E: int):
+    """q/k/v weights either packed `in_proj_weight` (kdim == embed_dim) or separate --
+    ttl/tell/modules/attention/multi_head.py:234-240, 488-526."""
+    b = sd[p + 'in_proj_bias']
+    if p + 'in_proj_weight' in sd:
+        w = sd[p + 'in_proj_weight']
+        wq, wk, wv = w[:E], w[E:2 * E], w[2 * E:]
+    else:
+        wq, wk, wv = sd[p + 'q_proj_weight'], sd[p + 'k_proj_weight'], sd[p + 'v_proj_weight']
+    return wq, wk, wv, b[:E], b[E:2 * E], b[2 * E:]
+
+
+def mha_project_kv(mem: torch.Tensor, sd: SD, p: str, E: int):
+    """K/V rows for one source incl. the learned bias row and the all-zero row:
+    k = [Wk m + bk ; bias_k ; 0]  -- multi_head.py:347-374, 416-421.  mem [S,B,kdim] -> [S+2,B,E]"""
+    _, wk, wv, _, bk, bv = mha_params(sd, p, E)
+    S, B, _ = mem.shape
+    k = F.linear(mem, wk, bk)
+    v = F.linear(mem, wv, bv)
+    z = mem.new_zeros(1, B, E)
+    k = torch.cat([k, sd[p + 'bias_k'].expand(1, B, E), z], 0)
+    v = torch.cat([v, sd[p + 'bias_v'].expand(1, B, E), z], 0)
+    return k, v
+
+
+def mha_attend(query: torch.Tensor, k: torch.Tensor, v: torch.Tensor, pad_mask: torch.Tensor,
+               sd: SD, p: str, H: int):
+    """softmax_fp32((Wq x + bq) * d^-1/2 . k^T + mask(-inf)) . v -> out_proj; also the
+    head-averaged probabilities [B,T,S+2] -- multi_head.py:348-353, 376-486."""
+    T, B, E = query.shape
+    D = E // H
+    wq, _, _, bq, _, _ = mha_params(sd, p, E)
+    q = F.linear(query, wq, bq) * (D ** -0.5)
+    S2 = k.shape[0]
+    qh = q.reshape(T, B, H, D).permute(1, 2, 0, 3)          # [B,H,T,D]
+    kh = k.reshape(S2, B, H, D).permute(1, 2, 0, 3)
+    vh = v.reshape(S2, B, H, D).permute(1, 2, 0, 3)
+    s = qh @ kh.transpose(-1, -2)                           # [B,H,T,S+2]
+    full_mask = torch.cat([pad_mask, pad_mask.new_zeros(B, 2)], 1)   # extra 2 keys never masked
+    s = s.masked_fill(full_mask[:, None, None, :], float('-inf'))
+    pr = torch.softmax(s.float(), -1).to(s.dtype)
+    o = (pr @ vh).permute(2, 0, 1, 3).reshape(T, B, E)
+    out = F.linear(o, sd[p + 'out_proj.weight'], sd[p + 'out_proj.bias'])
+    return out, pr.sum(1) / H
+
+
+def mha(query, mem, pad_mask, sd: SD, p: str, H: int):
+    k, v = mha_project_kv(mem, sd, p, query.shape[-1])
+    return mha_attend(query, k, v, pad_mask, sd, p, H)
+
+
+# ----------------------------------------------------------------------------- decoder layer
+def decoder_layer(X: torch.Tensor, contexts: dict, sd: SD, p: str, H: int, K: int,
+                  sources: Sequence[str], conv_hist: Optional[list] = None, kv_cache=None):
+    """DynamicConvDecoderLayer.forward, post-LN (decoder_normalize_before = false) --
+    ttl/tell/models/decoder_flattened.py:271-345 (2 sources),
+    ttl/tell/models/decoder_faces_objects.py:283-393 (4 sources; concat order image, article,
+    faces, obj).  `conv_hist` is a 1-element list holding the incremental conv buffer."""
+    res = X
+    h = F.glu(gehring_linear(X, sd, p + 'linear1.'), dim=-1)
+    w_tap = sd[p + 'conv.weight_linear.weight']
+    if conv_hist is None:
+        h = dynamic_conv(h, w_tap, H, K)
+    else:
+        h, conv_hist[0] = dynamic_conv_step(h, conv_hist[0], w_tap, H, K)
+    X = layer_norm(res + gehring_linear(h, sd, p + 'linear2.'), sd, p + 'conv_layer_norm.')
+
+    outs, attn = [], None
+    for s in sources:
+        ap = p + 'context_attns.%s.' % s
+        if kv_cache is not None and (p, s) in kv_cache:
+            k, v = kv_cache[(p, s)]
+        else:
+            k, v = mha_project_kv(contexts[s], sd, ap, X.shape[-1])
+            if kv_cache is not None:
+                kv_cache[(p, s)] = (k, v)
+        a, w = mha_attend(X, k, v, contexts[s + '_mask'], sd, ap, H)
+        if s == 'article':
+            attn = w
+        outs.append(layer_norm(X + a, sd, p + 'context_attn_lns.%s.' % s))
+    X = gehring_linear(torch.cat(outs, -1), sd, p + 'context_fc.')
+    f = gehring_linear(F.relu(gehring_linear(X, sd, p + 'fc1.')), sd, p + 'fc2.')
+    X = layer_norm(X + f, sd, p + 'final_layer_norm.')
+    return X, attn
+
+
+# ----------------------------------------------------------------------------- embedder
+def sinusoid_table(n: int, d: int, padding_idx: int = 1) -> torch.Tensor:
+    """tensor2tensor sinusoids [sin | cos], row `padding_idx` zeroed --
+    ttl/tell/modules/token_embedders/positional.py:125-165."""
+    half = d // 2
+    inc = math.log(10000.0) / (half - 1)
+    inv = torch.exp(torch.arange(half, dtype=torch.float) * -inc)
+    ang = torch.arange(n, dtype=torch.float)[:, None] * inv[None, :]
+    tab = torch.cat([ang.sin(), ang.cos()], 1)
+    tab[padding_idx] = 0
+    return tab
+
+
+def embed(ids: torch.Tensor, sd: SD, cutoffs: Sequence[int], start_pos: int = 0,
+          p: str = 'embedder.') -> torch.Tensor:
+    """SumTextFieldEmbedder(adaptive + sinusoidal position).
+    adaptive: band i row (id - cutoff[i-1]) of Embedding_i, times Linear_i, times sqrt(d); the
+    band-local row 0 is the nn.Embedding padding row (zeros) -- adaptive.py:36-76.
+    position: pad ids (==1) -> table row 1 (zeros); else column index + 2 + start_pos --
+    positional.py:167-211, 231-268; sum -- sum_text_field_embedder.py:117."""
+    B, T = ids.shape
+    d = sd[p + 'token_embedder_adaptive.embeddings.0.1.weight'].shape[0]
+    out = torch.zeros(B, T, d)
+    lo = 0
+    for i, hi in enumerate(cutoffs):
+        m = (ids >= lo) & (ids < hi)
+        if m.any():
+            e = sd[p + 'token_embedder_adaptive.embeddings.%d.0.weight' % i]
+            pr = sd[p + 'token_embedder_adaptive.embeddings.%d.1.weight' % i]
+            out[m] = F.linear(e[ids[m] - lo], pr)
+        lo = hi
+    out = out * math.sqrt(d)
+    tab = sd[p + 'token_embedder_position.weights']
+    pos = torch.arange(T)[None, :].expand(B, T) + 2 + start_pos
+    pos = torch.where(ids == 1, torch.ones_like(pos), pos)
+    return out + tab[pos]
+
+
+# ----------------------------------------------------------------------------- adaptive softmax
+def head_weight(sd: SD, p: str = 'adaptive_softmax.') -> torch.Tensor:
+    """TiedHeadModule: [tied band-0 embedding ; class_proj] -- softmax.py:11-40."""
+    return torch.cat([sd[p + 'head.word_proj.weight'], sd[p + 'head.class_proj.weight']], 0)
+
+
+def adaptive_targets(target: torch.Tensor, cutoffs: Sequence[int]):
+    """adapt_target -- softmax.py:144-167. Returns head target [N] and per tail (rows, local ids)."""
+    t = target.reshape(-1)
+    head_t = t.clone()
+    tails = []
+    for i in range(len(cutoffs) - 1):
+        m = (t >= cutoffs[i]) & (t < cutoffs[i + 1])
+        head_t[m] = cutoffs[0] + i
+        tails.append((m.nonzero().squeeze(1), t[m] - cutoffs[i]))
+    return head_t, tails
+
+
+def adaptive_nll(x: torch.Tensor, target: torch.Tensor, sd: SD, cutoffs: Sequence[int],
+                 pad: int = 1, p: str = 'adaptive_softmax.'):
+    """AdaptiveSoftmax.forward + AdaptiveLoss.forward(reduction='sum') --
+    softmax.py:169-191, criteria/adaptive_loss.py:27-73.  NB ignore_index=pad is applied INSIDE
+    every cluster, so tail-local id 1 (tokens cutoff[i]+1) contributes no tail term.
+    Returns (loss_sum, n_nonpad_tokens)."""
+    X = x.reshape(-1, x.shape[-1])
+    head_t, tails = adaptive_targets(target, cutoffs)
+    loss = F.cross_entropy(F.linear(X, head_weight(sd, p)), head_t, ignore_index=pad,
+                           reduction='sum')
+    for i, (rows, loc) in enumerate(tails):
+        if rows.numel():
+            z = F.linear(F.linear(X[rows], sd[p + 'tail.%d.0.weight' % i]),
+                         sd[p + 'tail.%d.2.weight' % i])
+            loss = loss + F.cross_entropy(z, loc, ignore_index=pad, reduction='sum')
+    return loss, int((target != pad).sum())
+
+
+def adaptive_log_prob(x: torch.Tensor, sd: SD, cutoffs: Sequence[int],
+                      p: str = 'adaptive_softmax.') -> torch.Tensor:
+    """get_log_prob: full-vocabulary log-probs -- softmax.py:193-222.  x [B,T,d] -> [B,T,V]"""
+    B, T, d = x.shape
+    X = x.reshape(-1, d)
+    hl = F.log_softmax(F.linear(X, head_weight(sd, p)), 1)
+    parts = [hl[:, :cutoffs[0]]]
+    for i in range(len(cutoffs) - 1):
+        z = F.linear(F.linear(X, sd[p + 'tail.%d.0.weight' % i]), sd[p + 'tail.%d.2.weight' % i])
+        parts.append(F.log_softmax(z, 1) + hl[:, cutoffs[0] + i, None])
+    return torch.cat(parts, 1).view(B, T, -1)
+
+
+# ----------------------------------------------------------------------------- whole decoder
+def n_layers(sd: SD) -> int:
+    return 1 + max(int(k.split('.')[1]) for k in sd if k.startswith('layers.'))
+
+
+def layer_kernel(sd: SD, i: int, H: int) -> int:
+    return sd['layers.%d.conv.weight_linear.weight' % i].shape[0] // H
+
+
+def decoder_forward(ids: torch.Tensor, contexts: dict, sd: SD, H: int, cutoffs: Sequence[int],
+                    sources: Sequence[str] = ('image', 'article'), state: Optional[dict] = None):
+    """DynamicConvDecoder.forward -- decoder_flattened.py:96-146 / decoder_faces_objects.py:95-144
+    (eval mode: every dropout is the identity).  ids [B,T] -> X [B,T,d], article attn [B,T,S+2].
+    `state` (dict) switches on the incremental path: position offset + per-layer conv buffers
+    (+ a K/V cache, which the reference recomputes each step -- same numbers)."""
+    start = 0
+    if state is not None:
+        start = state.get('pos', 0)
+        state['pos'] = start + ids.shape[1]
+    X = embed(ids, sd, cutoffs, start).transpose(0, 1)
+    attn = None
+    for i in range(n_layers(sd)):
+        hist = None
+        if state is not None:
+            hist = state.setdefault(('conv', i), [None])
+        X, attn = decoder_layer(X, contexts, sd, 'layers.%d.' % i, H, layer_kernel(sd, i, H),
+                                sources, hist, None if state is None else state.setdefault('kv', {}))
+    return X.transpose(0, 1), attn
+
+
+def greedy_generate(seed_ids: torch.Tensor, contexts: dict, sd: SD, H: int,
+                    cutoffs: Sequence[int], sources=('image', 'article'), gen_len: int = 100,
+                    eos: int = 2, pad: int = 1):
+    """`_generate` with sampling_topk=1 (= arg-max) -- ttl/tell/models/transformer_flattened.py:
+    238-325 / transformer_faces_objects.py:399-494.  Finished rows are dropped from the batch
+    (here: masked, which is numerically identical since rows are independent); outputs are padded
+    with `pad` ids / 0 log-probs.  Returns (log_probs [B,L], token_ids [B,L+1])."""
+    B = seed_ids.shape[0]
+    state: dict = {}
+    active = seed_ids[:, -1] != eos
+    toks, lps = [seed_ids[:, :1]], []
+    cur = seed_ids[:, :1]
+    for _ in range(gen_len):
+        X, _ = decoder_forward(cur, contexts, sd, H, cutoffs, sources, state)
+        lp = adaptive_log_prob(X[:, -1:], sd, cutoffs)[:, 0]
+        best_lp, best = lp.max(-1)
+        tok = torch.where(active, best, torch.full_like(best, pad))
+        lps.append(torch.where(active, best_lp, torch.zeros_like(best_lp))[:, None])
+        toks.append(tok[:, None])
+        active = active & (best != eos)
+        cur = best[:, None]
+        if not bool(active.any()):
+            break
+    return torch.cat(lps, 1), torch.cat(toks, 1)
+
+
+# ----------------------------------------------------------------------------- final*/transformer_v2
+def v2_layer_norm(x, a, b, eps=1e-6):
+    """final*/transformer_v2.py:82-94: UNBIASED std, eps added to the std (outside the sqrt)."""
+    mu = x.mean(-1, keepdim=True)
+    sdv = x.std(-1, keepdim=True)
+    return a * (x - mu) / (sdv + eps) + b
+
+
+def v2_mha(query, mem, mask, sd: SD, p: str, h: int):
+    """MultiHeadedAttention.forward + attention() -- final_roberta2/transformer_v2.py:213-266.
+    scores/sqrt(d_k), masked_fill(mask == 0, -1e9), softmax, PV, output linear.
+    query [B,T,d]; mem [B,S,d_key]; mask broadcastable to [B,1,T,S] or None."""
+    B, T, d = query.shape
+    dk = d // h
+    q = F.linear(query, sd[p + 'linears.0.weight'], sd[p + 'linears.0.bias'])
+    k = F.linear(mem, sd[p + 'linear_kv.0.weight'], sd[p + 'linear_kv.0.bias'])
+    v = F.linear(mem, sd[p + 'linear_kv.1.weight'], sd[p + 'linear_kv.1.bias'])
+    q = q.view(B, T, h, dk).transpose(1, 2)
+    k = k.view(B, -1, h, dk).transpose(1, 2)
+    v = v.view(B, -1, h, dk).transpose(1, 2)
+    s = q @ k.transpose(-1, -2) / math.sqrt(dk)
+    if mask is not None:
+        s = s.masked_fill(mask.unsqueeze(1) == 0, -1e9)
+    o = (F.softmax(s, -1) @ v).transpose(1, 2).reshape(B, T, d)
+    return F.linear(o, sd[p + 'linears.1.weight'], sd[p + 'linears.1.bias'])
+
+
+def v2_decoder_layer(x, memory, tgt_mask, sd: SD, p: str, h: int):
+    """DecoderLayer.forward, pre-norm SublayerConnection (x + sublayer(norm(x))) --
+    final_roberta2/transformer_v2.py:96-109, 186-211.  img-attn and article-attn both read the
+    post-self-attention x; their residual outputs are concatenated into context_fc."""
+    def nrm(t, i):
+        return v2_layer_norm(t, sd[p + 'sublayer.%d.norm.a_2' % i], sd[p + 'sublayer.%d.norm.b_2' % i])
+    n = nrm(x, 0)
+    x = x + v2_mha(n, n, tgt_mask, sd, p + 'self_attn.', h)
+    xi = x + v2_mha(nrm(x, 1), memory['image'], None, sd, p + 'img_attn.', h)
+    xa = x + v2_mha(nrm(x, 2), memory['article'], memory.get('article_mask'), sd,
+                    p + 'article_attn.', h)
+    x = F.linear(torch.cat([xi, xa], -1), sd[p + 'context_fc.weight'], sd[p + 'context_fc.bias'])
+    n = nrm(x, 3)
+    f = F.linear(F.relu(F.linear(n, sd[p + 'feed_forward.w_1.weight'], sd[p + 'feed_forward.w_1.bias'])),
+                 sd[p + 'feed_forward.w_2.weight'], sd[p + 'feed_forward.w_2.bias'])
+    return x + f
+
+
+def v2_positional(T: int, d: int) -> torch.Tensor:
+    """PositionalEncoding: interleaved sin/cos -- final_roberta2/transformer_v2.py (PositionalEncoding)."""
+    pe = torch.zeros(T, d)
+    pos = torch.arange(0, T, dtype=torch.float).unsqueeze(1)
+    div = torch.exp(torch.arange(0, d, 2).float() * -(math.log(10000.0) / d))
+    pe[:, 0::2] = torch.sin(pos * div)
+    pe[:, 1::2] = torch.cos(pos * div)
+    return pe
+
+
+def v2_decode(ids, memory, tgt_mask, sd: SD, h: int):
+    """OnlyDecoder.decode: Embeddings(x sqrt d) + PositionalEncoding -> N layers -> LayerNorm --
+    final_roberta2/transformer_v2.py:45-51, 111-140."""
+    lut = sd['tgt_embed.0.lut.weight']
+    d = lut.shape[1]
+    x = lut[ids] * math.sqrt(d) + v2_positional(ids.shape[1], d)[None]
+    L = 1 + max(int(k.split('.')[2]) for k in sd if k.startswith('decoder.layers.'))
+    for i in range(L):
+        x = v2_decoder_layer(x, memory, tgt_mask, sd, 'decoder.layers.%d.' % i, h)
+    return v2_layer_norm(x, sd['decoder.norm.a_2'], sd['decoder.norm.b_2'])
+
+
+def v2_generator_loss(out, y, sd: SD, pad: int, norm: float):
+    """Generator.proj + CrossEntropyLoss(ignore_index=pad, reduction='sum') / norm --
+    final_roberta2/transformer_v2.py:54-62, final_roberta2/custom_v4.py:404-419."""
+    z = F.linear(out, sd['generator.proj.weight'], sd['generator.proj.bias'])
+    return F.cross_entropy(z.reshape(-1, z.shape[-1]), y.reshape(-1), ignore_index=pad,
+                           reduction='sum') / norm
+
+
+def v2_subsequent_mask(T: int) -> torch.Tensor:
+    """final_roberta2/transformer_v2.py:391-397: lower-triangular (incl. diagonal) = visible."""
+    return torch.tril(torch.ones(1, T, T, dtype=torch.bool))
+
+
+def v2_translate(memory, sd: SD, h: int, max_len: int, bos: int = 0):
+    """translate_sentence: fixed max_len-1 greedy steps, whole prefix re-decoded each step,
+    no EOS stop -- final_roberta2/custom_v4.py:647-662."""
+    B = memory['image'].shape[0]
+    ys = torch.full((B, 1), bos, dtype=torch.long)
+    for _ in range(max_len - 1):
+        out = v2_decode(ys, memory, v2_subsequent_mask(ys.shape[1]), sd, h)
+        z = F.linear(out[:, -1], sd['generator.proj.weight'], sd['generator.proj.bias'])
+        ys = torch.cat([ys, F.log_softmax(z, -1).argmax(-1, keepdim=True)], 1)
+    return ys
