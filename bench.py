@@ -1,0 +1,283 @@
+#!/usr/bin/env python
+"""Benchmark of the caption-decoder hot path (BASELINE.json metric: decoder tokens/sec & captions/sec).
+
+Workload (configs[1]): Transform-and-Tell decoder, 4 layers, d=1024, 16 heads, DynamicConv K=3/7/15/31,
+2 sources (49 image feats x 2048, 512 RoBERTa tokens x 1024), caption length 32, batch 64 PER GPU, bf16,
+teacher-forced forward + AdaptiveSoftmax loss over the 50265-BPE vocabulary.  Synthetic inputs, random
+init weights (no dataset / checkpoint offline).  One step = one pass over one batch.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+B_PER_GPU, T, S_IMG, S_ART, VOCAB = 64, 32, 49, 512, 50265
+WORKLOAD = 'tell-decoder-2src L4 d1024 H16 K3/7/15/31 V50265 fwd+adaptive-loss B64/gpu T32 S49+512'
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get('hbm_gbs', 6650.0), d.get('bf16_tflops', 1590.0), d.get('bf16_tflops_sustained', 1400.0), 'measured'
+    return 6650.0, 1590.0, 1400.0, 'fallback'
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clocks and throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self._halt = index, [], set(), None, threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonSwPowerCap: 'sw_power_cap',
+                 nv.nvmlClocksThrottleReasonHwSlowdown: 'hw_slowdown',
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: 'sw_thermal_slowdown',
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: 'hw_thermal_slowdown',
+                 nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: 'hw_power_brake'}
+        while not self._halt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, n in names.items():
+                    if r & bit:
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=1)
+        s = sorted(self.samples)
+        return {'sm_mhz': s[len(s) // 2] if s else None, 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons)}
+
+
+def make_inputs(seed):
+    from oracle import synth          # pure torch input generator shared with the tests (no reference code)
+    return synth.make_batch(B_PER_GPU, T, VOCAB, ('image', 'article'), seed=seed, S_img=S_IMG, S_art=S_ART)
+
+
+def cpu_baseline_run(sd, cfg, n_iters, B):
+    """The oracle port (CPU restatement of the reference modules) on this box's host cores: forward +
+    AdaptiveLoss at B captions.  Returns (tokens/s, seconds per iteration list)."""
+    from oracle import restate as O
+    from oracle import synth
+    prev, tgt, ctx = synth.make_batch(B, T, VOCAB, ('image', 'article'), seed=4321, S_img=S_IMG, S_art=S_ART)
+    ntok = int((tgt != 1).sum())
+    times = []
+    with torch.no_grad():
+        for i in range(n_iters + 1):
+            t0 = time.perf_counter()
+            X, _ = O.decoder_forward(prev, ctx, sd, cfg['heads'], cfg['cutoffs'], cfg['sources'])
+            O.adaptive_nll(X, tgt, sd, cfg['cutoffs'])
+            dt = time.perf_counter() - t0
+            if i > 0:                      # first iteration = warm-up
+                times.append(dt)
+    med = sorted(times)[len(times) // 2]
+    return ntok / med, med, ntok
+
+
+def run_reference(args, rank):
+    """--impl reference: the reference's CPU implementation of the path (the Python reference cannot travel
+    to the GPU box, so its restatement oracle/restate.py -- pinned against it -- is what runs)."""
+    if rank != 0:
+        return
+    from news_image_caption_b200.decoder import random_state_dict
+    cores = len(os.sched_getaffinity(0))
+    torch.set_num_threads(cores)
+    cfg = dict(heads=16, cutoffs=[5000, 20000, VOCAB], sources=['image', 'article'])
+    sd = random_state_dict(seed=0)
+    Bs = 4
+    from oracle import restate as O
+    from oracle import synth
+    prev, tgt, ctx = synth.make_batch(Bs, T, VOCAB, ('image', 'article'), seed=4321, S_img=S_IMG, S_art=S_ART)
+    ntok = int((tgt != 1).sum())
+
+    def step():
+        with torch.no_grad():
+            X, _ = O.decoder_forward(prev, ctx, sd, 16, cfg['cutoffs'], cfg['sources'])
+            return O.adaptive_nll(X, tgt, sd, cfg['cutoffs'])
+    for _ in range(max(1, min(args.warmup, 2))):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    v = ntok * args.steps / dt
+    print(json.dumps({
+        'impl': 'reference', 'metric': 'decoder_tokens_per_sec', 'value': v, 'unit': 'tokens/s', 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * dt / args.steps, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': WORKLOAD, 'sample': 'B=%d captions per step on the host CPU' % Bs},
+        'captions_per_sec': Bs * args.steps / dt,
+        'cpu_baseline': {'value': v, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port',
+                         'sample': 'oracle port, fp32, B=%d T=32 fwd+loss, %d steps' % (Bs, args.steps)},
+        'e2e': {'value': v, 'unit': 'tokens/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    if args.impl == 'reference':
+        return run_reference(args, rank)
+    args.warmup = max(args.warmup, 3)
+
+    import torch.distributed as dist
+    from news_image_caption_b200 import DynamicConvDecoder, _lib, build
+    from news_image_caption_b200 import ops
+    from news_image_caption_b200.decoder import random_state_dict
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    if rank == 0:
+        build.build()
+    if world > 1:
+        dist.barrier()
+    _lib.require_device()
+    L = _lib.lib()
+
+    sd = random_state_dict(seed=0)
+    dec = DynamicConvDecoder(dtype=torch.bfloat16)
+    dec.load_reference_state_dict(sd)
+    dec.prepare()
+    prev, tgt, ctx = make_inputs(1234 + rank)                     # batch shard of this rank (weak scaling)
+    ntok = int((tgt != 1).sum())
+    prev_d, tgt_d = prev.cuda(), tgt.cuda()
+    ctx_d = {k: (v.cuda().bfloat16() if v.is_floating_point() else v.cuda()) for k, v in ctx.items()}
+    # host-side (pinned) copies for the end-to-end arm
+    pin = lambda t: t.contiguous().pin_memory()
+    prev_h, tgt_h = pin(prev), pin(tgt)
+    ctx_h = {k: pin(v.bfloat16() if v.is_floating_point() else v) for k, v in ctx.items()}
+    h2d = prev_h.numel() * 8 * 2 + sum(v.numel() * v.element_size() for v in ctx_h.values())
+
+    def step():
+        X, _ = dec(prev_d, ctx_d, need_attn=False)
+        return dec.nll(X, tgt_d)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        out = step()
+    loss_check = out.cpu()
+    sync_all()
+    sampler = ClockSampler(local)
+    sampler.start()
+    n0 = L.tnt_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    sync_all()
+    launches = L.tnt_launch_count() - n0
+    clocks = sampler.stop()
+    ms = torch.tensor([e0.elapsed_time(e1)], device='cuda')
+    ntok_all = torch.tensor([float(ntok)], device='cuda')
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ntok_all)
+    ms_total = ms.item()
+    value = ntok_all.item() * args.steps / (ms_total * 1e-3)
+
+    # ---- end to end: pinned host buffers -> C ABI (H2D + forward + loss + D2H), every step
+    for _ in range(2):
+        dec.score_host(prev_h, tgt_h, ctx_h)
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        l_h, n_h = dec.score_host(prev_h, tgt_h, ctx_h)
+    e2e_s = torch.tensor([time.perf_counter() - t0], device='cuda')
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = ntok_all.item() * args.steps / e2e_s.item()
+    assert abs(l_h - loss_check[0].item()) < 1e-3 * abs(l_h) and int(n_h) == ntok, (l_h, loss_check, n_h, ntok)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel: the tcgen05 GEMM that projects K/V of the article for all layers
+    hbm, tf_burst, tf_sus, which = peaks()
+    M, N, K = S_ART * B_PER_GPU, 4 * 2 * 1024, 1024
+    a = torch.randn(M, K, device='cuda').bfloat16()
+    w = (torch.randn(N, K, device='cuda') / 32).bfloat16()
+    b = torch.zeros(N, device='cuda')
+    for _ in range(3):
+        ops.linear(a, w, b)
+    torch.cuda.synchronize()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 10
+    g0.record()
+    for _ in range(reps):
+        ops.linear(a, w, b)
+    g1.record()
+    torch.cuda.synchronize()
+    gemm_ms = g0.elapsed_time(g1) / reps
+    flops = 2.0 * M * N * K
+    achieved = flops / (gemm_ms * 1e-3) / 1e12
+    roofline = {'bound': 'tensor', 'kernel': 'gemm_tc_kernel<EPI_NONE,bf16> (article K/V projection, all layers)',
+                'achieved': achieved, 'peak': tf_burst, 'unit': 'TFLOP/s', 'frac': achieved / tf_burst,
+                'traffic': None, 'peak_source': which + ' bf16_tflops (burst: kernel timed alone)',
+                'shape': [M, N, K], 'ms_per_launch': gemm_ms,
+                'share_of_step': gemm_ms / (ms_total / args.steps)}
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        cores = len(os.sched_getaffinity(0))
+        torch.set_num_threads(cores)
+        cfg = dict(heads=16, cutoffs=[5000, 20000, VOCAB], sources=['image', 'article'])
+        v, med, nt = cpu_baseline_run(sd, cfg, 3, 4)
+        cpu = {'value': v, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port',
+               'sample': 'oracle port (restated reference modules), fp32, B=4 T=32 fwd+loss, median of 3 (%.2f s/iter)' % med}
+
+    print(json.dumps({
+        'metric': 'decoder_tokens_per_sec', 'value': value, 'unit': 'tokens/s', 'n_gpus': world, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': ms_total / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+        'config': {'workload': WORKLOAD, 'l2': 'per-step working set (K/V 0.5 GB + activations) exceeds the 126 MB L2',
+                   'non_pad_tokens_per_step_per_gpu': ntok},
+        'captions_per_sec': B_PER_GPU * world * args.steps / (ms_total * 1e-3),
+        'e2e': {'value': e2e_value, 'unit': 'tokens/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 8,
+                'captions_per_sec': B_PER_GPU * world * args.steps / e2e_s.item()},
+        'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roofline, 'cpu_baseline': cpu}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

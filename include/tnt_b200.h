@@ -1,0 +1,316 @@
+/* tnt_b200.h -- C ABI of the B200-native caption-decoder hot path ("Transform-and-Tell" decoder).
+ *
+ * The reference (harsh157/news_image_caption) has no FFI of its own: its plugin boundary is the
+ * Python nn.Module contract + the AllenNLP registry.  This header is the
+ * boundary a replacement sits UNDER: every entry point is extern "C", takes plain device pointers,
+ * sizes and a stream, allocates nothing, never throws, and returns 0 or a negative tnt_status.
+ * Each entry point cites the reference interface it replaces (paths relative to the reference root).
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers unless the name ends in _host;
+ *   - activations are row-major [rows, cols] with an explicit leading dimension in ELEMENTS;
+ *     decoder-layer tensors use the reference's T x B x C order (row = t * B + b);
+ *   - dtype: TNT_F32 or TNT_BF16 for activations and GEMM weights; biases, LayerNorm parameters,
+ *     softmax statistics, losses and log-probabilities are always fp32; ids are int64 (torch.long);
+ *   - `stream` is a cudaStream_t passed as void*; calls are stream-ordered and never synchronise
+ *     (the *_host entry points are the exception and say so);
+ *   - the caller owns every buffer; workspaces are sized by the matching *_workspace_bytes query.
+ */
+#ifndef TNT_B200_H_
+#define TNT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* tnt_stream;
+
+typedef enum { TNT_F32 = 0, TNT_BF16 = 1 } tnt_dtype;
+
+typedef enum {
+  TNT_OK = 0,
+  TNT_ERR_ARG = -1,       /* bad shape / null pointer / unsupported combination */
+  TNT_ERR_ALIGN = -2,     /* pointer or leading dimension not aligned for the vector / TMA path */
+  TNT_ERR_CUDA = -3,      /* a CUDA runtime / driver call failed; see tnt_last_error() */
+  TNT_ERR_WORKSPACE = -4, /* workspace too small */
+  TNT_ERR_NODEVICE = -5   /* no sm_100 device */
+} tnt_status;
+
+int tnt_version(void);
+const char* tnt_last_error(void);          /* thread-local message of the last failing call */
+int tnt_device_check(void);                /* TNT_OK iff the current device is sm_100 */
+
+/* ------------------------------------------------------------------------------------------
+ * Linear layers.  Replaces GehringLinear / TiedLinear / F.linear call sites:
+ *   ttl/tell/modules/linear.py:7-50, multi_head.py:488-526 (in_proj_*), softmax.py:99-132.
+ * C[M,N] = epilogue(A[M,K] . W[N,K]^T + bias[N]).  W uses the nn.Linear layout.
+ * bf16: hand-written tcgen05 + TMA kernel (fp32 accumulate in TMEM); fp32: SIMT fp32 kernel.
+ * ------------------------------------------------------------------------------------------ */
+typedef enum {
+  TNT_EPI_NONE = 0,      /* + bias (if any) */
+  TNT_EPI_RELU = 1,      /* relu(acc + bias)                       decoder_flattened.py:338 */
+  TNT_EPI_GLU = 2,       /* W rows pair-interleaved (a0,b0,a1,b1..): out[:, j] = a_j * sigmoid(b_j);
+                            N counts the interleaved rows, C has N/2 columns.  decoder_flattened.py:284-286 */
+  TNT_EPI_RESIDUAL = 3   /* acc + bias + residual[M,N]             decoder_flattened.py:288-291 */
+} tnt_epilogue;
+
+typedef struct {
+  const void* a;  int64_t lda;        /* [M,K]  dtype_in */
+  const void* w;  int64_t ldw;        /* [N,K]  dtype_in */
+  const float* bias;                  /* [N] or NULL */
+  const void* residual; int64_t ldr;  /* [M,N'] dtype_out, TNT_EPI_RESIDUAL only */
+  void* c;        int64_t ldc;        /* [M,N'] dtype_out */
+  int M, N, K;
+  const int* m_dyn;                   /* optional DEVICE row count (<= M): rows >= *m_dyn are skipped */
+  /* grouped problems sharing M,N,K (e.g. one per attention source); element strides, 0 = shared */
+  int groups;
+  int64_t stride_a, stride_w, stride_bias, stride_res, stride_c;
+  int dtype_in, dtype_out, epilogue;
+} tnt_linear_params;
+int tnt_linear_fwd(const tnt_linear_params* p, tnt_stream stream);
+
+/* weight_norm fold w = g * v / ||v||_row (linear.py:30-33, nn.utils.weight_norm dim=0), optional
+ * GLU pair-interleave of the output rows, cast to `dtype_out`.  g may be NULL (plain cast/copy). */
+int tnt_wn_fold(const float* v, const float* g, void* w_out, int rows, int cols, int glu_interleave,
+                int dtype_out, tnt_stream stream);
+/* bias companion of the GLU interleave: b_out[2j] = b[j], b_out[2j+1] = b[j + n/2] */
+int tnt_glu_interleave_bias(const float* b, float* b_out, int n, tnt_stream stream);
+int tnt_cast(const void* src, void* dst, int64_t n, int dtype_src, int dtype_dst, tnt_stream stream);
+
+/* ------------------------------------------------------------------------------------------
+ * DynamicConv1dTBC (causal, weight_softmax, padding_l = K-1, no renorm, no bias).
+ *   ttl/tell/modules/convolutions/dynamic.py:85-120,285-336 (forward / _forward_expanded),
+ *   :95-99,114-116,338-348 (incremental input buffer).
+ * y[t,b,h*R+r] = sum_j softmax_K(logits[t,b,h,:])[j] * x[t-(K-1)+j, b, h*R+r],  x[<0] := history or 0.
+ * The softmax runs over ALL K taps; taps reaching before the start are dropped, not renormalised.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const void* x;  int64_t ldx;        /* [T*B, C] conv input (the GLU output) */
+  const void* logits; int64_t ldl;    /* [T*B, H*K] tap logits = weight_linear(x) */
+  void* y;        int64_t ldy;        /* [T*B, C] */
+  /* incremental decoding: the last `hist_len` (<= K-1) conv inputs, oldest first, [hist_len*B, C];
+     NULL for teacher forcing.  If hist_out != NULL the updated window (last min(K-1, hist_len+T)
+     inputs) is written there (may alias hist only if hist_len + T <= K-1 is false ... see DESIGN). */
+  const void* hist; int hist_len;
+  int T, B, C, H, K;
+  int dtype;
+} tnt_dynconv_params;
+int tnt_dynconv_fwd(const tnt_dynconv_params* p, tnt_stream stream);
+
+typedef struct {
+  const void* x;  int64_t ldx;        /* forward input  [T*B, C] */
+  const void* logits; int64_t ldl;    /* forward logits [T*B, H*K] */
+  const void* dy; int64_t lddy;       /* [T*B, C] */
+  void* dx;       int64_t lddx;       /* [T*B, C]   gradient through the value path only */
+  void* dlogits;  int64_t lddl;       /* [T*B, H*K] gradient w.r.t. the tap logits */
+  int T, B, C, H, K;
+  int dtype;
+} tnt_dynconv_bwd_params;
+int tnt_dynconv_bwd(const tnt_dynconv_bwd_params* p, tnt_stream stream);
+
+/* single-step ring buffer form used by the generation engine (kernel group 5):
+ * ring [K-1, B, C] holds conv inputs of steps pos-K+1 .. pos-1 at slot (step mod (K-1)); the new
+ * input is consumed and then stored at slot pos mod (K-1). */
+typedef struct {
+  const void* x;  int64_t ldx;        /* [B, C] */
+  const void* logits; int64_t ldl;    /* [B, H*K] */
+  void* y;        int64_t ldy;        /* [B, C] */
+  void* ring;                          /* [(K-1), B, C] */
+  const int* pos;                      /* DEVICE step counter (number of inputs already seen) */
+  int B, C, H, K;
+  int dtype;
+} tnt_dynconv_step_params;
+int tnt_dynconv_step(const tnt_dynconv_step_params* p, tnt_stream stream);
+
+/* ------------------------------------------------------------------------------------------
+ * LayerNorm over the last dimension of [rows, C] (fp32 statistics).
+ *   nn.LayerNorm: decoder_flattened.py:245-268 (variant 0: biased var, eps inside sqrt)
+ *   final* LayerNorm: final_roberta2/transformer_v2.py:82-94 (variant 1: unbiased std, eps outside)
+ * `groups` > 1 : row r uses gamma/beta block (r % groups) -- the per-source context_attn_lns.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const void* x; int64_t ldx;
+  void* y;       int64_t ldy;
+  const float* gamma; const float* beta;   /* [groups, C] */
+  int rows, C, groups, variant;
+  float eps;
+  int dtype;
+  /* optional transposed store: output row r = (t*B+b) is written to row (b*T+t); 0 = off */
+  int transpose_T, transpose_B;
+} tnt_layernorm_params;
+int tnt_layernorm_fwd(const tnt_layernorm_params* p, tnt_stream stream);
+
+typedef struct {
+  const void* x; int64_t ldx;     /* forward input */
+  const void* dy; int64_t lddy;
+  void* dx; int64_t lddx;
+  const float* gamma;
+  float* dgamma; float* dbeta;    /* [C] fp32, accumulated with atomics (must be zeroed) */
+  int rows, C;
+  float eps;
+  int dtype;
+} tnt_layernorm_bwd_params;
+int tnt_layernorm_bwd(const tnt_layernorm_bwd_params* p, tnt_stream stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Token + position embedding.
+ *   AdaptiveEmbedding  ttl/tell/modules/token_embedders/adaptive.py:61-76   (band table . proj * sqrt(d))
+ *   Sinusoidal         ttl/tell/modules/token_embedders/positional.py:167-211,231-268
+ *   Sum                ttl/tell/modules/token_embedders/sum_text_field_embedder.py:97-118
+ * The per-band projection is pre-multiplied at load time (table_i . proj_i^T * sqrt(d)), so the
+ * forward is a pure gather: out[t*B+b] = table[ids[b,t]] + pos_table[ids==pad ? pad : t+pad+1+start].
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const int64_t* ids;            /* [B, T] */
+  const void* table;             /* [V, d] pre-projected, pre-scaled */
+  const float* pos_table;        /* [n_pos, d] */
+  void* out; int64_t ldo;        /* [T*B, d] (T x B x C order) */
+  const int* start_pos;          /* DEVICE incremental offset or NULL (0) */
+  int B, T, d, n_pos, pad_idx;
+  int dtype;
+} tnt_embed_params;
+int tnt_embed_fwd(const tnt_embed_params* p, tnt_stream stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Multi-head cross attention over one or more memory sources.
+ *   ttl/tell/modules/attention/multi_head.py:288-486 (manual path, static_kv)
+ *   final_roberta2/transformer_v2.py:213-266        (attention(), MultiHeadedAttention)
+ * Inputs are the PROJECTED q / k / v.  Per (b, h):  softmax_fp32(scale * q k^T + mask) v.
+ * tell semantics (n_extra = 2): two extra keys after the S memory rows -- the learned
+ * bias_k/bias_v row and an all-zero row -- never masked (multi_head.py:355-374,416-427).
+ * ------------------------------------------------------------------------------------------ */
+typedef enum {
+  TNT_MASK_NONE = 0,
+  TNT_MASK_KEY_PADDING = 1,   /* mask[b, s] != 0  -> -inf            (multi_head.py:441-449) */
+  TNT_MASK_V2 = 2             /* mask[b, t, s] == 0 -> -1e9          (transformer_v2.py:217-218) */
+} tnt_mask_mode;
+
+typedef struct {
+  const void* q;  int64_t q_stride_t, q_stride_b;    /* element strides; head h at column h*D */
+  const void* k;  int64_t k_stride_s, k_stride_b;
+  const void* v;  int64_t v_stride_s, v_stride_b;
+  void* out;      int64_t o_stride_t, o_stride_b;
+  const uint8_t* mask; int64_t m_stride_b, m_stride_t; /* bytes, innermost stride over s is 1 */
+  const float* bias_k; const float* bias_v;          /* [H*D] fp32, n_extra == 2 only */
+  float* weights;     /* optional [B, T, S + n_extra] fp32 head-AVERAGED probabilities (multi_head.py:478-482) */
+  int B, T, S, H, D;
+  int n_extra, mask_mode;
+  float scale;
+  int dtype;
+} tnt_xattn_params;
+int tnt_xattn_fwd(const tnt_xattn_params* p, tnt_stream stream);
+
+
+
+/* ------------------------------------------------------------------------------------------
+ * AdaptiveSoftmax + AdaptiveLoss.
+ *   ttl/tell/modules/softmax.py:144-222, ttl/tell/modules/criteria/adaptive_loss.py:27-73
+ *   (= final_roberta2/adaptive_loss.py:25-70);  Generator+CE final_roberta2/transformer_v2.py:54-62 is the
+ *   single-cluster case (n_clusters = 1).
+ * One cluster = logits z = Xp . W^T (+bias) over `n_cols` classes.  The kernels never write z:
+ *   stats[r] = (max, sum exp(z - max), argmax, z[target]) per row.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  const void* x; int64_t ldx;     /* [M, K] */
+  const void* w; int64_t ldw;     /* [n_cols, K] */
+  const float* bias;              /* [n_cols] or NULL */
+  const int* target;              /* [M] cluster-local target column or -1; may be NULL */
+  const int* row_map;             /* optional [M]: stats row index for gathered inputs */
+  const int* m_dyn;               /* optional DEVICE row count */
+  float* stats;                   /* [rows, 4] : max, sum exp(z-max), argmax (int bits), target logit */
+  void* workspace; size_t workspace_bytes;
+  int M, n_cols, K;
+  int dtype;
+} tnt_lse_params;
+size_t tnt_lse_workspace_bytes(int M, int n_cols, int dtype);
+int tnt_lse_fwd(const tnt_lse_params* p, tnt_stream stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Decoder engine: the whole DynamicConvDecoder forward, loss, log-probs and greedy generation.
+ *   DynamicConvDecoder.forward      ttl/tell/models/decoder_flattened.py:96-146
+ *   DynamicConvDecoderLayer.forward ttl/tell/models/decoder_flattened.py:271-345,
+ *                                   ttl/tell/models/decoder_faces_objects.py:283-393
+ *   get_normalized_probs            ttl/tell/models/decoder_flattened.py:187-200
+ *   _generate (greedy, top-1)       ttl/tell/models/transformer_flattened.py:238-325,
+ *                                   ttl/tell/models/transformer_faces_objects.py:399-494
+ * Weights are loaded under the reference's own state_dict keys (fp32 device tensors), so a
+ * reference checkpoint is the input format.
+ * ------------------------------------------------------------------------------------------ */
+#define TNT_MAX_SOURCES 4
+#define TNT_MAX_LAYERS 16
+#define TNT_MAX_CLUSTERS 4
+
+typedef struct {
+  int n_layers, d, heads, ffn, vocab;
+  int kernels[TNT_MAX_LAYERS];
+  int n_sources;
+  char source_names[TNT_MAX_SOURCES][16];  /* concat order, e.g. image, article, faces, obj */
+  int source_dim[TNT_MAX_SOURCES];
+  int n_clusters;                          /* head + tails */
+  int cutoffs[TNT_MAX_CLUSTERS];           /* cumulative: [5000, 20000, 50265] */
+  int pad_idx;                             /* 1: positions + loss ignore_index */
+  int max_positions;                       /* rows of the sinusoid table */
+  int dtype;                               /* TNT_BF16 or TNT_F32 (parity mode) */
+} tnt_decoder_config;
+
+typedef struct tnt_decoder tnt_decoder;
+
+tnt_decoder* tnt_decoder_create(const tnt_decoder_config* cfg);
+void tnt_decoder_destroy(tnt_decoder* d);
+/* bytes of DEVICE memory the prepared (folded / cast / fused) weights need */
+size_t tnt_decoder_weight_bytes(const tnt_decoder* d);
+int tnt_decoder_bind_weights(tnt_decoder* d, void* weight_mem, size_t bytes);
+/* feed one reference state_dict entry (fp32, device, contiguous).  Unknown keys return TNT_ERR_ARG. */
+int tnt_decoder_load(tnt_decoder* d, const char* key, const float* data, const int64_t* shape, int ndim,
+                     tnt_stream stream);
+/* fold weight-norm, fuse per-source projections, pre-project the embedding bands */
+int tnt_decoder_finalize(tnt_decoder* d, tnt_stream stream);
+
+typedef struct {
+  int B, T;
+  int S[TNT_MAX_SOURCES];
+  const void* memory[TNT_MAX_SOURCES];      /* [S, B, source_dim] engine dtype (reference layout) */
+  const uint8_t* pad_mask[TNT_MAX_SOURCES]; /* [B, S] bool, nonzero = padding */
+} tnt_contexts;
+
+size_t tnt_decoder_workspace_bytes(const tnt_decoder* d, int B, int T, const int* S);
+/* workspace of tnt_decoder_nll / tnt_decoder_log_prob for n_rows rows */
+size_t tnt_decoder_loss_workspace_bytes(const tnt_decoder* d, int n_rows);
+
+/* teacher-forced forward.  ids [B,T] -> X [B,T,d] (engine dtype); attn optional [B,T,S_article+2] fp32 */
+int tnt_decoder_forward(tnt_decoder* d, const int64_t* ids, const tnt_contexts* ctx, void* X_out,
+                        float* attn_out, void* workspace, size_t workspace_bytes, tnt_stream stream);
+/* AdaptiveLoss(reduction='sum'): out[0] = loss sum (nats), out[1] = number of non-pad targets */
+int tnt_decoder_nll(tnt_decoder* d, const void* X, const int64_t* target, int n_rows, float* out2,
+                    void* workspace, size_t workspace_bytes, tnt_stream stream);
+/* AdaptiveSoftmax.get_log_prob: [n_rows, vocab] fp32 */
+int tnt_decoder_log_prob(tnt_decoder* d, const void* X, int n_rows, float* out, void* workspace,
+                         size_t workspace_bytes, tnt_stream stream);
+/* greedy generation with incremental DynamicConv state and cached K/V.
+ * seed [B] first token; ids_out [B, gen_len+1] (col 0 = seed, finished rows padded with pad_idx);
+ * logp_out [B, gen_len] (0 after the row finished).  Runs all steps; returns in *steps_host (may be
+ * NULL) the number of steps after which every row had finished (host sync only if non-NULL). */
+size_t tnt_decoder_generate_workspace_bytes(const tnt_decoder* d, int B, int gen_len, const int* S);
+int tnt_decoder_generate(tnt_decoder* d, const int64_t* seed, const tnt_contexts* ctx, int gen_len, int eos,
+                         int64_t* ids_out, float* logp_out, int* steps_host, void* workspace,
+                         size_t workspace_bytes, tnt_stream stream);
+
+/* End-to-end convenience used for the e2e benchmark: ids/targets/contexts/masks in PINNED HOST
+ * memory, loss read back; performs the H2D copies, forward, loss and D2H on `stream` and
+ * synchronises it.  staging = device buffer of tnt_decoder_score_host_staging_bytes(). */
+size_t tnt_decoder_score_host_staging_bytes(const tnt_decoder* d, int B, int T, const int* S);
+int tnt_decoder_score_host(tnt_decoder* d, const int64_t* ids_host, const int64_t* target_host,
+                           const tnt_contexts* ctx_host, float* out2_host, void* staging,
+                           size_t staging_bytes, void* workspace, size_t workspace_bytes,
+                           tnt_stream stream);
+
+/* number of kernels this library has launched since load (for bench.py's gpu_launches) */
+uint64_t tnt_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TNT_B200_H_ */

@@ -1,0 +1,8 @@
+"""B200-native (sm_100a) caption-decoder hot path of the Transform-and-Tell derivative
+harsh157/news_image_caption: hand-written CUDA kernels behind a C ABI (include/tnt_b200.h) and a
+host-side mirror of the reference's decoder / loss module interface.  No CPU fallback."""
+from . import _lib  # noqa: F401
+from ._lib import TntError, lib, require_device  # noqa: F401
+from .decoder import AdaptiveLoss, DynamicConvDecoder  # noqa: F401
+
+__all__ = ['DynamicConvDecoder', 'AdaptiveLoss', 'lib', 'require_device', 'TntError']

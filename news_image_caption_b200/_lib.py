@@ -1,0 +1,152 @@
+"""ctypes binding of libtnt_b200.so (include/tnt_b200.h).  No torch types cross this boundary: only raw
+device pointers, sizes and the CUDA stream handle.  Loading fails loudly -- there is no CPU fallback."""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, 'libtnt_b200.so')
+
+TNT_F32, TNT_BF16 = 0, 1
+EPI_NONE, EPI_RELU, EPI_GLU, EPI_RESIDUAL = 0, 1, 2, 3
+MASK_NONE, MASK_KEY_PADDING, MASK_V2 = 0, 1, 2
+MAX_SOURCES, MAX_LAYERS, MAX_CLUSTERS = 4, 16, 4
+
+vp, i64, i32, f32 = C.c_void_p, C.c_int64, C.c_int, C.c_float
+
+
+class TntError(RuntimeError):
+    pass
+
+
+class LinearParams(C.Structure):
+    _fields_ = [('a', vp), ('lda', i64), ('w', vp), ('ldw', i64), ('bias', vp), ('residual', vp), ('ldr', i64),
+                ('c', vp), ('ldc', i64), ('M', i32), ('N', i32), ('K', i32), ('m_dyn', vp), ('groups', i32),
+                ('stride_a', i64), ('stride_w', i64), ('stride_bias', i64), ('stride_res', i64), ('stride_c', i64),
+                ('dtype_in', i32), ('dtype_out', i32), ('epilogue', i32)]
+
+
+class DynconvParams(C.Structure):
+    _fields_ = [('x', vp), ('ldx', i64), ('logits', vp), ('ldl', i64), ('y', vp), ('ldy', i64), ('hist', vp),
+                ('hist_len', i32), ('T', i32), ('B', i32), ('C', i32), ('H', i32), ('K', i32), ('dtype', i32)]
+
+
+class DynconvBwdParams(C.Structure):
+    _fields_ = [('x', vp), ('ldx', i64), ('logits', vp), ('ldl', i64), ('dy', vp), ('lddy', i64), ('dx', vp),
+                ('lddx', i64), ('dlogits', vp), ('lddl', i64), ('T', i32), ('B', i32), ('C', i32), ('H', i32),
+                ('K', i32), ('dtype', i32)]
+
+
+class DynconvStepParams(C.Structure):
+    _fields_ = [('x', vp), ('ldx', i64), ('logits', vp), ('ldl', i64), ('y', vp), ('ldy', i64), ('ring', vp),
+                ('pos', vp), ('B', i32), ('C', i32), ('H', i32), ('K', i32), ('dtype', i32)]
+
+
+class LayernormParams(C.Structure):
+    _fields_ = [('x', vp), ('ldx', i64), ('y', vp), ('ldy', i64), ('gamma', vp), ('beta', vp), ('rows', i32),
+                ('C', i32), ('groups', i32), ('variant', i32), ('eps', f32), ('dtype', i32), ('transpose_T', i32),
+                ('transpose_B', i32)]
+
+
+class LayernormBwdParams(C.Structure):
+    _fields_ = [('x', vp), ('ldx', i64), ('dy', vp), ('lddy', i64), ('dx', vp), ('lddx', i64), ('gamma', vp),
+                ('dgamma', vp), ('dbeta', vp), ('rows', i32), ('C', i32), ('eps', f32), ('dtype', i32)]
+
+
+class EmbedParams(C.Structure):
+    _fields_ = [('ids', vp), ('table', vp), ('pos_table', vp), ('out', vp), ('ldo', i64), ('start_pos', vp),
+                ('B', i32), ('T', i32), ('d', i32), ('n_pos', i32), ('pad_idx', i32), ('dtype', i32)]
+
+
+class XattnParams(C.Structure):
+    _fields_ = [('q', vp), ('q_stride_t', i64), ('q_stride_b', i64), ('k', vp), ('k_stride_s', i64),
+                ('k_stride_b', i64), ('v', vp), ('v_stride_s', i64), ('v_stride_b', i64), ('out', vp),
+                ('o_stride_t', i64), ('o_stride_b', i64), ('mask', vp), ('m_stride_b', i64), ('m_stride_t', i64),
+                ('bias_k', vp), ('bias_v', vp), ('weights', vp), ('B', i32), ('T', i32), ('S', i32), ('H', i32),
+                ('D', i32), ('n_extra', i32), ('mask_mode', i32), ('scale', f32), ('dtype', i32)]
+
+
+class LseParams(C.Structure):
+    _fields_ = [('x', vp), ('ldx', i64), ('w', vp), ('ldw', i64), ('bias', vp), ('target', vp), ('row_map', vp),
+                ('m_dyn', vp), ('stats', vp), ('workspace', vp), ('workspace_bytes', C.c_size_t), ('M', i32),
+                ('n_cols', i32), ('K', i32), ('dtype', i32)]
+
+
+class DecoderConfig(C.Structure):
+    _fields_ = [('n_layers', i32), ('d', i32), ('heads', i32), ('ffn', i32), ('vocab', i32),
+                ('kernels', i32 * MAX_LAYERS), ('n_sources', i32), ('source_names', (C.c_char * 16) * MAX_SOURCES),
+                ('source_dim', i32 * MAX_SOURCES), ('n_clusters', i32), ('cutoffs', i32 * MAX_CLUSTERS),
+                ('pad_idx', i32), ('max_positions', i32), ('dtype', i32)]
+
+
+class Contexts(C.Structure):
+    _fields_ = [('B', i32), ('T', i32), ('S', i32 * MAX_SOURCES), ('memory', vp * MAX_SOURCES),
+                ('pad_mask', vp * MAX_SOURCES)]
+
+
+_SIGS = {
+    'tnt_version': (i32, []),
+    'tnt_last_error': (C.c_char_p, []),
+    'tnt_device_check': (i32, []),
+    'tnt_launch_count': (C.c_uint64, []),
+    'tnt_linear_fwd': (i32, [C.POINTER(LinearParams), vp]),
+    'tnt_wn_fold': (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
+    'tnt_glu_interleave_bias': (i32, [vp, vp, i32, vp]),
+    'tnt_cast': (i32, [vp, vp, i64, i32, i32, vp]),
+    'tnt_dynconv_fwd': (i32, [C.POINTER(DynconvParams), vp]),
+    'tnt_dynconv_bwd': (i32, [C.POINTER(DynconvBwdParams), vp]),
+    'tnt_dynconv_step': (i32, [C.POINTER(DynconvStepParams), vp]),
+    'tnt_layernorm_fwd': (i32, [C.POINTER(LayernormParams), vp]),
+    'tnt_layernorm_bwd': (i32, [C.POINTER(LayernormBwdParams), vp]),
+    'tnt_embed_fwd': (i32, [C.POINTER(EmbedParams), vp]),
+    'tnt_xattn_fwd': (i32, [C.POINTER(XattnParams), vp]),
+    'tnt_lse_workspace_bytes': (C.c_size_t, [i32, i32, i32]),
+    'tnt_lse_fwd': (i32, [C.POINTER(LseParams), vp]),
+    'tnt_decoder_create': (vp, [C.POINTER(DecoderConfig)]),
+    'tnt_decoder_destroy': (None, [vp]),
+    'tnt_decoder_weight_bytes': (C.c_size_t, [vp]),
+    'tnt_decoder_bind_weights': (i32, [vp, vp, C.c_size_t]),
+    'tnt_decoder_load': (i32, [vp, C.c_char_p, vp, C.POINTER(i64), i32, vp]),
+    'tnt_decoder_finalize': (i32, [vp, vp]),
+    'tnt_decoder_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
+    'tnt_decoder_loss_workspace_bytes': (C.c_size_t, [vp, i32]),
+    'tnt_decoder_forward': (i32, [vp, vp, C.POINTER(Contexts), vp, vp, vp, C.c_size_t, vp]),
+    'tnt_decoder_nll': (i32, [vp, vp, vp, i32, vp, vp, C.c_size_t, vp]),
+    'tnt_decoder_log_prob': (i32, [vp, vp, i32, vp, vp, C.c_size_t, vp]),
+    'tnt_decoder_generate_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
+    'tnt_decoder_generate': (i32, [vp, vp, C.POINTER(Contexts), i32, i32, vp, vp, C.POINTER(i32), vp, C.c_size_t, vp]),
+    'tnt_decoder_score_host_staging_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
+    'tnt_decoder_score_host': (i32, [vp, vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp, C.c_size_t, vp]),
+    'tnt_debug_force_simt_gemm': (None, [i32]),
+}
+
+_lib = None
+
+
+def exported_symbols():
+    """Every entry point include/tnt_b200.h declares (plus the one debug hook)."""
+    return sorted(_SIGS)
+
+
+def lib():
+    """Loads the CUDA library; raises if it has not been built (python -m news_image_caption_b200.build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise TntError('libtnt_b200.so is missing: run `python news_image_caption_b200/build.py` '
+                           '(there is no CPU fallback)')
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(L, name)           # AttributeError if the symbol is not exported
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(status, what=''):
+    if status != 0:
+        msg = lib().tnt_last_error().decode('utf-8', 'replace')
+        raise TntError('%s failed (%d): %s' % (what or 'tnt call', status, msg))
+
+
+def require_device():
+    check(lib().tnt_device_check(), 'tnt_device_check')

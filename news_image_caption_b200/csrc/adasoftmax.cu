@@ -1,0 +1,369 @@
+// AdaptiveSoftmax head + AdaptiveLoss (kernel group 3): cluster log-sum-exp / NLL / arg-max computed in
+// the GEMM epilogue (gemm.cu, EPI_LSE) -- logits are never written -- plus the small finishing kernels.
+// Reference: ttl/tell/modules/softmax.py:144-222 (adapt_target, forward, get_log_prob),
+//            ttl/tell/modules/criteria/adaptive_loss.py:27-73, final_roberta2/adaptive_loss.py:25-70.
+#include "adasoftmax.cuh"
+
+#include <algorithm>
+
+namespace tnt {
+namespace {
+
+// merge the per-N-tile partials of one row: one warp per row
+__global__ void __launch_bounds__(256) lse_finish_kernel(const float4* partials, int n_tiles, int M, const int* m_dyn,
+                                                         const int* row_map, float4* stats) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int Me = m_dyn ? min(M, *m_dyn) : M;
+  if (row >= Me) return;
+  LseAcc a;
+  a.init();
+  for (int t = lane; t < n_tiles; t += 32) {
+    const float4 p = partials[static_cast<long>(row) * n_tiles + t];
+    a.merge(p.x, p.y, __float_as_int(p.z), p.w);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float m2 = __shfl_xor_sync(0xffffffffu, a.m, o), s2 = __shfl_xor_sync(0xffffffffu, a.s, o);
+    const float t2 = __shfl_xor_sync(0xffffffffu, a.tz, o);
+    const int a2 = __shfl_xor_sync(0xffffffffu, a.arg, o);
+    a.merge(m2, s2, a2, t2);
+  }
+  if (lane == 0) stats[row_map ? row_map[row] : row] = make_float4(a.m, a.s, __int_as_float(a.arg), a.tz);
+}
+
+// adapt_target (softmax.py:144-167): head targets + ordered per-tail row lists.  Single CTA -> the
+// row order inside each tail is the reference's (ascending), so results are run-to-run identical.
+__global__ void __launch_bounds__(1024) adapt_target_kernel(const int64_t* target, int N, AdaCuts c, int* head_t,
+                                                            int* tail_rows, int* tail_loc, int* counts) {
+  __shared__ int warp_cnt[TNT_MAX_CLUSTERS][32];
+  __shared__ int base[TNT_MAX_CLUSTERS];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x < TNT_MAX_CLUSTERS) base[threadIdx.x] = 0;
+  __syncthreads();
+  for (int r0 = 0; r0 < N; r0 += 1024) {
+    const int r = r0 + threadIdx.x;
+    const long t = r < N ? target[r] : -1;
+    int band = -1;
+    if (r < N) {
+      int ht = static_cast<int>(t);
+      for (int i = 1; i < c.n; ++i)
+        if (t >= c.cut[i - 1] && t < c.cut[i]) { band = i - 1; ht = c.cut[0] + i - 1; }
+      head_t[r] = ht;
+    }
+    unsigned mybal = 0;
+    for (int i = 0; i < c.n - 1; ++i) {
+      const unsigned bal = __ballot_sync(0xffffffffu, band == i);
+      if (band == i) mybal = bal;
+      if (lane == 0) warp_cnt[i][warp] = __popc(bal);
+    }
+    __syncthreads();
+    if (band >= 0) {
+      int off = base[band];
+      for (int w = 0; w < warp; ++w) off += warp_cnt[band][w];
+      off += __popc(mybal & ((1u << lane) - 1));   // rank among the warp's lanes of the same band
+      tail_rows[static_cast<long>(band) * N + off] = r;
+      tail_loc[static_cast<long>(band) * N + off] = static_cast<int>(t - c.cut[band]);
+    }
+    __syncthreads();
+    if (threadIdx.x < c.n - 1) {
+      int s = 0;
+      for (int w = 0; w < 32; ++w) s += warp_cnt[threadIdx.x][w];
+      base[threadIdx.x] += s;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x < c.n - 1) counts[threadIdx.x] = base[threadIdx.x];
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) gather_rows_kernel(const T* x, long ldx, const int* rows, const int* count, int d,
+                                                          T* out) {
+  const int lane = threadIdx.x & 31;
+  const int n = *count;
+  for (int j = blockIdx.x * 8 + (threadIdx.x >> 5); j < n; j += gridDim.x * 8) {
+    const T* s = x + static_cast<long>(rows[j]) * ldx;
+    T* o = out + static_cast<long>(j) * d;
+    for (int vc = lane; vc < (d >> 3); vc += 32) {
+      float v[8];
+      load8(s + vc * 8, v);
+      store8(o + vc * 8, v);
+    }
+  }
+}
+
+__device__ __forceinline__ float head_lse(const float4 st, const float* side, int n_tails) {
+  float M = st.x;
+  for (int i = 0; i < n_tails; ++i) M = fmaxf(M, side[i]);
+  float s = st.y * __expf(st.x - M);
+  for (int i = 0; i < n_tails; ++i) s += __expf(side[i] - M);
+  return M + __logf(s);
+}
+
+// AdaptiveLoss(reduction='sum') (adaptive_loss.py:55-65): deterministic single-CTA reduction.
+__global__ void __launch_bounds__(1024) nll_reduce_kernel(const int64_t* target, const int* head_t, int N, AdaCuts c,
+                                                          int pad, const float4* head_stats, const float* side,
+                                                          const float4* tail_stats, const int* tail_loc,
+                                                          const int* counts, float* out2) {
+  __shared__ float red[32];
+  float loss = 0.f, ntok = 0.f;
+  const int nt = c.n - 1;
+  for (int r = threadIdx.x; r < N; r += 1024) {
+    if (target[r] != pad) ntok += 1.f;
+    const int ht = head_t[r];
+    if (ht != pad) {                                    // ignore_index inside the head cluster
+      const float lse = head_lse(head_stats[r], side + static_cast<long>(r) * nt, nt);
+      const float zt = ht < c.cut[0] ? head_stats[r].w : side[static_cast<long>(r) * nt + ht - c.cut[0]];
+      loss += lse - zt;
+    }
+  }
+  for (int i = 0; i < nt; ++i) {
+    const int n = counts[i];
+    for (int j = threadIdx.x; j < n; j += 1024) {
+      if (tail_loc[static_cast<long>(i) * N + j] != pad) {  // ignore_index inside the tail (local id 1)
+        const float4 st = tail_stats[static_cast<long>(i) * N + j];
+        loss += st.x + __logf(st.y) - st.w;
+      }
+    }
+  }
+  loss = block_sum(loss, red);
+  ntok = block_sum(ntok, red);
+  if (threadIdx.x == 0) {
+    out2[0] = loss;
+    out2[1] = ntok;
+  }
+}
+
+// greedy pick: arg-max over the full vocabulary of get_log_prob (softmax.py:193-222) without building it
+__global__ void __launch_bounds__(256) greedy_pick_kernel(int N, AdaCuts c, const float4* head_stats, const float* side,
+                                                          const float4* tail_stats, int64_t* tok, float* logp) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= N) return;
+  const int nt = c.n - 1;
+  const float4 hs = head_stats[r];
+  const float lse = head_lse(hs, side + static_cast<long>(r) * nt, nt);
+  float best = hs.x - lse;
+  long arg = __float_as_int(hs.z);
+  for (int i = 0; i < nt; ++i) {
+    const float4 ts = tail_stats[static_cast<long>(i) * N + r];
+    const float lp = side[static_cast<long>(r) * nt + i] - lse - __logf(ts.y);   // prior + (max - lse_tail)
+    if (lp > best) {
+      best = lp;
+      arg = c.cut[i] + __float_as_int(ts.z);
+    }
+  }
+  tok[r] = arg;
+  logp[r] = best;
+}
+
+// get_log_prob finishing pass over materialised logits: out row = [head words | tail_0 | tail_1 ...]
+// `head` [N, cut0 + nt] raw head logits (scratch); tails already sit raw in `out`.
+__global__ void __launch_bounds__(256) logprob_norm_kernel(int N, AdaCuts c, const float* head, float* out) {
+  __shared__ float red[32];
+  __shared__ float bc;
+  const int r = blockIdx.x, nt = c.n - 1, nh = c.cut[0] + nt, V = c.cut[c.n - 1];
+  const float* h = head + static_cast<long>(r) * nh;
+  float* o = out + static_cast<long>(r) * V;
+  float m = -INFINITY;
+  for (int i = threadIdx.x; i < nh; i += blockDim.x) m = fmaxf(m, h[i]);
+  m = warp_max(m);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = red[0];
+    for (int w = 1; w < (blockDim.x >> 5); ++w) t = fmaxf(t, red[w]);
+    bc = t;
+  }
+  __syncthreads();
+  m = bc;
+  float s = 0.f;
+  for (int i = threadIdx.x; i < nh; i += blockDim.x) s += __expf(h[i] - m);
+  s = block_sum(s, red);
+  const float lse = m + logf(s);
+  for (int i = threadIdx.x; i < c.cut[0]; i += blockDim.x) o[i] = h[i] - lse;
+  for (int k = 0; k < nt; ++k) {
+    const float prior = h[c.cut[0] + k] - lse;
+    float* z = o + c.cut[k];
+    const int n = c.cut[k + 1] - c.cut[k];
+    float tm = -INFINITY;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) tm = fmaxf(tm, z[i]);
+    tm = warp_max(tm);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = tm;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = red[0];
+      for (int w = 1; w < (blockDim.x >> 5); ++w) t = fmaxf(t, red[w]);
+      bc = t;
+    }
+    __syncthreads();
+    tm = bc;
+    float ts = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) ts += __expf(z[i] - tm);
+    ts = block_sum(ts, red);
+    const float sub = tm + logf(ts) - prior;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) z[i] -= sub;
+  }
+}
+
+inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
+
+}  // namespace
+
+int lse_gemm(const void* x, long ldx, const void* w, long ldw, const float* bias, int M, int n_cols, int K, int dtype,
+             const int* m_dyn, const int* target, const int* row_map, int n_lse, float* side, long side_ld,
+             float4* partials, float4* stats, cudaStream_t st) {
+  tnt_linear_params lp = {};
+  lp.a = x; lp.lda = ldx; lp.w = w; lp.ldw = ldw; lp.bias = bias;
+  lp.M = M; lp.N = n_cols; lp.K = K; lp.m_dyn = m_dyn; lp.groups = 1;
+  lp.dtype_in = dtype; lp.dtype_out = TNT_F32; lp.epilogue = EPI_LSE;
+  LseExtra ex = {target, partials, n_lse, side, side_ld};
+  int n_tiles = 0;
+  TNT_TRY(launch_gemm(&lp, EPI_LSE, &ex, &n_tiles, st));
+  lse_finish_kernel<<<(M + 7) / 8, 256, 0, st>>>(partials, n_tiles, M, m_dyn, row_map, stats);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+size_t lse_partials_bytes(int M, int n_cols) { return al256(static_cast<size_t>(M) * ((n_cols + 31) / 32) * sizeof(float4)); }
+
+// ---------------------------------------------------------------------------- workspace layout
+struct AdaWs {
+  int* head_t; int* tail_rows; int* tail_loc; int* counts;
+  float4* head_stats; float* side; float4* tail_stats; float4* partials;
+  void* xc; void* proj; float* head_raw;
+  size_t total;
+};
+
+static AdaWs carve(const AdaSoftmax& a, int N, void* ws, bool need_raw) {
+  AdaWs w;
+  const int nt = a.cuts.n - 1;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = ws ? static_cast<char*>(ws) + off : nullptr;
+    off += al256(bytes);
+    return p;
+  };
+  int max_cols = a.cuts.cut[0] + nt;
+  for (int i = 0; i < nt; ++i) max_cols = std::max(max_cols, a.cuts.cut[i + 1] - a.cuts.cut[i]);
+  w.head_t = static_cast<int*>(take(sizeof(int) * N));
+  w.tail_rows = static_cast<int*>(take(sizeof(int) * N * std::max(nt, 1)));
+  w.tail_loc = static_cast<int*>(take(sizeof(int) * N * std::max(nt, 1)));
+  w.counts = static_cast<int*>(take(sizeof(int) * TNT_MAX_CLUSTERS));
+  w.head_stats = static_cast<float4*>(take(sizeof(float4) * N));
+  w.side = static_cast<float*>(take(sizeof(float) * N * std::max(nt, 1)));
+  w.tail_stats = static_cast<float4*>(take(sizeof(float4) * N * std::max(nt, 1)));
+  w.partials = static_cast<float4*>(take(lse_partials_bytes(N, max_cols)));
+  w.xc = take(dtype_size(a.dtype) * N * a.d);
+  w.proj = take(dtype_size(a.dtype) * N * a.d);
+  w.head_raw = need_raw ? static_cast<float*>(take(sizeof(float) * N * (a.cuts.cut[0] + nt))) : nullptr;
+  w.total = off;
+  return w;
+}
+
+size_t adasoftmax_workspace_bytes(const AdaSoftmax& a, int N, bool logprob) { return carve(a, N, nullptr, logprob).total; }
+
+static int tail_proj(const AdaSoftmax& a, int i, const void* x, long ldx, int M, const int* m_dyn, void* out,
+                     cudaStream_t st) {
+  tnt_linear_params lp = {};
+  lp.a = x; lp.lda = ldx; lp.w = a.proj_w[i]; lp.ldw = a.d; lp.c = out; lp.ldc = a.d;
+  lp.M = M; lp.N = a.d; lp.K = a.d; lp.m_dyn = m_dyn; lp.groups = 1;
+  lp.dtype_in = a.dtype; lp.dtype_out = a.dtype; lp.epilogue = EPI_NONE;
+  return launch_gemm(&lp, -1, nullptr, nullptr, st);
+}
+
+int adasoftmax_nll(const AdaSoftmax& a, const void* x, long ldx, const int64_t* target, int N, int pad, float* out2,
+                   void* ws, size_t ws_bytes, cudaStream_t st) {
+  AdaWs w = carve(a, N, ws, false);
+  if (w.total > ws_bytes) {
+    set_error("adasoftmax_nll: workspace %zu < %zu", ws_bytes, w.total);
+    return TNT_ERR_WORKSPACE;
+  }
+  const int nt = a.cuts.n - 1;
+  adapt_target_kernel<<<1, 1024, 0, st>>>(target, N, a.cuts, w.head_t, w.tail_rows, w.tail_loc, w.counts);
+  TNT_LAUNCHED();
+  TNT_TRY(lse_gemm(x, ldx, a.head_w, a.d, nullptr, N, a.cuts.cut[0] + nt, a.d, a.dtype, nullptr, w.head_t, nullptr,
+                   a.cuts.cut[0], w.side, nt, w.partials, w.head_stats, st));
+  for (int i = 0; i < nt; ++i) {
+    const int grid = std::min((N + 7) / 8, 4 * num_sms());
+    if (a.dtype == TNT_BF16)
+      gather_rows_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<const bf16*>(x), ldx, w.tail_rows + static_cast<long>(i) * N,
+                                                     w.counts + i, a.d, static_cast<bf16*>(w.xc));
+    else
+      gather_rows_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(x), ldx,
+                                                      w.tail_rows + static_cast<long>(i) * N, w.counts + i, a.d,
+                                                      static_cast<float*>(w.xc));
+    TNT_LAUNCHED();
+    TNT_TRY(tail_proj(a, i, w.xc, a.d, N, w.counts + i, w.proj, st));
+    const int ncols = a.cuts.cut[i + 1] - a.cuts.cut[i];
+    TNT_TRY(lse_gemm(w.proj, a.d, a.out_w[i], a.d, nullptr, N, ncols, a.d, a.dtype, w.counts + i,
+                     w.tail_loc + static_cast<long>(i) * N, nullptr, ncols, nullptr, 0, w.partials,
+                     w.tail_stats + static_cast<long>(i) * N, st));
+  }
+  nll_reduce_kernel<<<1, 1024, 0, st>>>(target, w.head_t, N, a.cuts, pad, w.head_stats, w.side, w.tail_stats, w.tail_loc,
+                                        w.counts, out2);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int adasoftmax_greedy(const AdaSoftmax& a, const void* x, long ldx, int N, int64_t* tok, float* logp, void* ws,
+                      size_t ws_bytes, cudaStream_t st) {
+  AdaWs w = carve(a, N, ws, false);
+  if (w.total > ws_bytes) {
+    set_error("adasoftmax_greedy: workspace %zu < %zu", ws_bytes, w.total);
+    return TNT_ERR_WORKSPACE;
+  }
+  const int nt = a.cuts.n - 1;
+  TNT_TRY(lse_gemm(x, ldx, a.head_w, a.d, nullptr, N, a.cuts.cut[0] + nt, a.d, a.dtype, nullptr, nullptr, nullptr,
+                   a.cuts.cut[0], w.side, nt, w.partials, w.head_stats, st));
+  for (int i = 0; i < nt; ++i) {
+    TNT_TRY(tail_proj(a, i, x, ldx, N, nullptr, w.proj, st));
+    const int ncols = a.cuts.cut[i + 1] - a.cuts.cut[i];
+    TNT_TRY(lse_gemm(w.proj, a.d, a.out_w[i], a.d, nullptr, N, ncols, a.d, a.dtype, nullptr, nullptr, nullptr, ncols,
+                     nullptr, 0, w.partials, w.tail_stats + static_cast<long>(i) * N, st));
+  }
+  greedy_pick_kernel<<<(N + 255) / 256, 256, 0, st>>>(N, a.cuts, w.head_stats, w.side, w.tail_stats, tok, logp);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int adasoftmax_logprob(const AdaSoftmax& a, const void* x, long ldx, int N, float* out, void* ws, size_t ws_bytes,
+                       cudaStream_t st) {
+  AdaWs w = carve(a, N, ws, true);
+  if (w.total > ws_bytes) {
+    set_error("adasoftmax_logprob: workspace %zu < %zu", ws_bytes, w.total);
+    return TNT_ERR_WORKSPACE;
+  }
+  const int nt = a.cuts.n - 1, V = a.cuts.cut[a.cuts.n - 1], nh = a.cuts.cut[0] + nt;
+  tnt_linear_params lp = {};
+  lp.a = x; lp.lda = ldx; lp.w = a.head_w; lp.ldw = a.d; lp.c = w.head_raw; lp.ldc = nh;
+  lp.M = N; lp.N = nh; lp.K = a.d; lp.groups = 1; lp.dtype_in = a.dtype; lp.dtype_out = TNT_F32; lp.epilogue = EPI_NONE;
+  TNT_TRY(launch_gemm(&lp, -1, nullptr, nullptr, st));
+  for (int i = 0; i < nt; ++i) {
+    TNT_TRY(tail_proj(a, i, x, ldx, N, nullptr, w.proj, st));
+    tnt_linear_params tp = {};
+    tp.a = w.proj; tp.lda = a.d; tp.w = a.out_w[i]; tp.ldw = a.d; tp.c = out + a.cuts.cut[i]; tp.ldc = V;
+    tp.M = N; tp.N = a.cuts.cut[i + 1] - a.cuts.cut[i]; tp.K = a.d; tp.groups = 1;
+    tp.dtype_in = a.dtype; tp.dtype_out = TNT_F32; tp.epilogue = EPI_NONE;
+    TNT_TRY(launch_gemm(&tp, -1, nullptr, nullptr, st));
+  }
+  logprob_norm_kernel<<<N, 256, 0, st>>>(N, a.cuts, w.head_raw, out);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+}  // namespace tnt
+
+extern "C" size_t tnt_lse_workspace_bytes(int M, int n_cols, int dtype) {
+  (void)dtype;
+  return tnt::lse_partials_bytes(M, n_cols);
+}
+
+extern "C" int tnt_lse_fwd(const tnt_lse_params* p, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(p && p->x && p->w && p->stats && p->workspace, "lse: null pointer");
+  TNT_CHECK_ARG(p->workspace_bytes >= lse_partials_bytes(p->M, p->n_cols), "lse: workspace too small");
+  return lse_gemm(p->x, p->ldx, p->w, p->ldw, p->bias, p->M, p->n_cols, p->K, p->dtype, p->m_dyn, p->target, p->row_map,
+                  p->n_cols, nullptr, 0, static_cast<float4*>(p->workspace), reinterpret_cast<float4*>(p->stats),
+                  as_stream(stream));
+}

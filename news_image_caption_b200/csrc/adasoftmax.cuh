@@ -1,0 +1,33 @@
+// Internal interface of the adaptive-softmax kernels (used by the engine and the C ABI).
+#pragma once
+#include "gemm.cuh"
+
+namespace tnt {
+
+struct AdaCuts {
+  int n;                          // clusters (head + tails)
+  int cut[TNT_MAX_CLUSTERS];      // cumulative cutoffs, cut[n-1] = vocab
+};
+
+struct AdaSoftmax {
+  AdaCuts cuts;
+  int d, dtype;
+  const void* head_w;                       // [cut0 + n_tails, d]  (tied band-0 embedding ; class_proj)
+  const void* proj_w[TNT_MAX_CLUSTERS];     // tail i: [d, d]
+  const void* out_w[TNT_MAX_CLUSTERS];      // tail i: [cut[i+1]-cut[i], d] (tied band embedding)
+};
+
+size_t lse_partials_bytes(int M, int n_cols);
+int lse_gemm(const void* x, long ldx, const void* w, long ldw, const float* bias, int M, int n_cols, int K, int dtype,
+             const int* m_dyn, const int* target, const int* row_map, int n_lse, float* side, long side_ld,
+             float4* partials, float4* stats, cudaStream_t st);
+
+size_t adasoftmax_workspace_bytes(const AdaSoftmax& a, int N, bool logprob);
+int adasoftmax_nll(const AdaSoftmax& a, const void* x, long ldx, const int64_t* target, int N, int pad, float* out2,
+                   void* ws, size_t ws_bytes, cudaStream_t st);
+int adasoftmax_greedy(const AdaSoftmax& a, const void* x, long ldx, int N, int64_t* tok, float* logp, void* ws,
+                      size_t ws_bytes, cudaStream_t st);
+int adasoftmax_logprob(const AdaSoftmax& a, const void* x, long ldx, int N, float* out, void* ws, size_t ws_bytes,
+                       cudaStream_t st);
+
+}  // namespace tnt

@@ -1,0 +1,319 @@
+// Causal DynamicConv1d (kernel group 1), its backward (group 4) and the single-step ring-buffer
+// form (group 5).  Reference: ttl/tell/modules/convolutions/dynamic.py:85-120,285-336,338-348.
+//
+// One CTA owns (batch row b, a group of heads, a tile of timesteps).  The conv-input window
+// [t0-(K-1), t0+TT) of that channel group is staged ONCE in shared memory (each input row is used by
+// K outputs), the K tap logits of every (t, head) are soft-maxed by a warp with shuffles into shared
+// memory, and each thread then produces 8 consecutive channels per timestep with 128-bit HBM
+// loads/stores.  HBM traffic = x once (+ a K-1 row halo per extra time tile) + logits once + y once.
+#include "common.cuh"
+
+namespace tnt {
+
+namespace {
+constexpr int kThreads = 256;
+constexpr int kTT = 32;           // timesteps per CTA tile
+
+// softmax over K logits of one (t, head) by one warp; result to smem taps[K]
+template <typename T>
+__device__ __forceinline__ void warp_softmax_taps(const T* lg, int K, float* out, int lane) {
+  float m = -INFINITY;
+  for (int j = lane; j < K; j += 32) m = fmaxf(m, to_f(lg[j]));
+  m = warp_max(m);
+  float s = 0.f;
+  for (int j = lane; j < K; j += 32) {
+    const float e = __expf(to_f(lg[j]) - m);
+    out[j] = e;
+    s += e;
+  }
+  s = warp_sum(s);
+  const float inv = 1.f / s;
+  for (int j = lane; j < K; j += 32) out[j] *= inv;
+}
+
+// ------------------------------------------------------------------------------ forward
+// smem: xs [(TT+K-1)][CC] fp32, taps [TT][HG][K] fp32
+template <typename T>
+__global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_params p, int CC, int HG) {
+  extern __shared__ float sm[];
+  const int K = p.K, R = p.C / p.H, B = p.B;
+  const int b = blockIdx.x, c0 = blockIdx.y * CC, t0 = blockIdx.z * kTT;
+  const int TT = min(kTT, p.T - t0);
+  const int rows = TT + K - 1;
+  float* xs = sm;
+  float* taps = sm + static_cast<size_t>(kTT + K - 1) * CC;
+  const T* x = reinterpret_cast<const T*>(p.x);
+  const T* hist = reinterpret_cast<const T*>(p.hist);
+  const T* lg = reinterpret_cast<const T*>(p.logits);
+  T* y = reinterpret_cast<T*>(p.y);
+  const int cc = min(CC, p.C - c0);
+  const int nv = cc >> 3;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // stage the input window (zeros / history before t = 0)
+  for (int i = threadIdx.x; i < rows * nv; i += kThreads) {
+    const int r = i / nv, vc = i - r * nv;
+    const int ts = t0 - (K - 1) + r;
+    float v[8];
+    if (ts >= 0) {
+      load8(x + (static_cast<long>(ts) * B + b) * p.ldx + c0 + vc * 8, v);
+    } else if (hist && p.hist_len + ts >= 0) {
+      load8(hist + (static_cast<long>(p.hist_len + ts) * B + b) * p.C + c0 + vc * 8, v);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = 0.f;
+    }
+    float* d = xs + r * CC + vc * 8;
+    *reinterpret_cast<float4*>(d) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(d + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  }
+  // taps
+  const int hg = cc / R, h0 = c0 / R;
+  for (int i = warp; i < TT * hg; i += kThreads / 32) {
+    const int t = i / hg, hl = i - t * hg;
+    warp_softmax_taps(lg + (static_cast<long>(t0 + t) * B + b) * p.ldl + (h0 + hl) * K, K,
+                      taps + (t * HG + hl) * K, lane);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < TT * nv; i += kThreads) {
+    const int t = i / nv, vc = i - t * nv;
+    const float* w = taps + (t * HG + (vc * 8) / R) * K;
+    const float* xr = xs + t * CC + vc * 8;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int j = 0; j < K; ++j) {
+      const float wj = w[j];
+      const float4 a = *reinterpret_cast<const float4*>(xr + j * CC);
+      const float4 c = *reinterpret_cast<const float4*>(xr + j * CC + 4);
+      acc[0] = fmaf(wj, a.x, acc[0]); acc[1] = fmaf(wj, a.y, acc[1]);
+      acc[2] = fmaf(wj, a.z, acc[2]); acc[3] = fmaf(wj, a.w, acc[3]);
+      acc[4] = fmaf(wj, c.x, acc[4]); acc[5] = fmaf(wj, c.y, acc[5]);
+      acc[6] = fmaf(wj, c.z, acc[6]); acc[7] = fmaf(wj, c.w, acc[7]);
+    }
+    store8(y + (static_cast<long>(t0 + t) * B + b) * p.ldy + c0 + vc * 8, acc);
+  }
+}
+
+// ------------------------------------------------------------------------------ single step
+// ring [K-1][B][C]; slot of step s = s mod (K-1).  One thread = 8 channels of one batch row.
+template <typename T>
+__global__ void __launch_bounds__(kThreads) dynconv_step_kernel(tnt_dynconv_step_params p) {
+  extern __shared__ float sm[];               // taps [H][K] of this batch row
+  const int K = p.K, R = p.C / p.H, b = blockIdx.x;
+  const int pos = p.pos ? *p.pos : 0;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const T* lg = reinterpret_cast<const T*>(p.logits) + static_cast<long>(b) * p.ldl;
+  for (int h = warp; h < p.H; h += kThreads / 32) warp_softmax_taps(lg + h * K, K, sm + h * K, lane);
+  __syncthreads();
+  const T* x = reinterpret_cast<const T*>(p.x) + static_cast<long>(b) * p.ldx;
+  T* y = reinterpret_cast<T*>(p.y) + static_cast<long>(b) * p.ldy;
+  T* ring = reinterpret_cast<T*>(p.ring);
+  const int nv = p.C >> 3, KM = K - 1;
+  for (int vc = threadIdx.x; vc < nv; vc += kThreads) {
+    const float* w = sm + ((vc * 8) / R) * K;
+    float xv[8], acc[8];
+    load8(x + vc * 8, xv);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = w[K - 1] * xv[i];
+    // tap j < K-1 multiplies the input of step pos-(K-1)+j
+    for (int j = 0; j < KM; ++j) {
+      const int s = pos - KM + j;
+      if (s < 0) continue;
+      float hv[8];
+      load8(ring + (static_cast<long>(s % KM) * p.B + b) * p.C + vc * 8, hv);
+      const float wj = w[j];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] = fmaf(wj, hv[i], acc[i]);
+    }
+    store8(y + vc * 8, acc);
+    if (KM > 0) store8(ring + (static_cast<long>(pos % KM) * p.B + b) * p.C + vc * 8, xv);
+  }
+}
+
+// ------------------------------------------------------------------------------ backward
+// smem: xs [(TT+K-1)][CCP] (inputs t0-(K-1) .. t0+TT-1), dys [(TT+K-1)][CCP] (grads t0 .. t0+TT+K-2),
+//       taps [(TT+K-1)][HG][K] for t0 .. t0+TT+K-2, dws [TT][HG][K]; CCP = CC + 1 (bank spread).
+template <typename T>
+__global__ void __launch_bounds__(kThreads) dynconv_bwd_kernel(tnt_dynconv_bwd_params p, int CC, int HG) {
+  extern __shared__ float sm[];
+  const int K = p.K, R = p.C / p.H, B = p.B, KM = K - 1;
+  const int b = blockIdx.x, c0 = blockIdx.y * CC, t0 = blockIdx.z * kTT;
+  const int TT = min(kTT, p.T - t0);
+  const int CCP = CC + 1;
+  const int rows = TT + KM;
+  float* xs = sm;
+  float* dys = xs + static_cast<size_t>(kTT + KM) * CCP;
+  float* taps = dys + static_cast<size_t>(kTT + KM) * CCP;
+  float* dws = taps + static_cast<size_t>(kTT + KM) * HG * K;
+  const T* x = reinterpret_cast<const T*>(p.x);
+  const T* dy = reinterpret_cast<const T*>(p.dy);
+  const T* lg = reinterpret_cast<const T*>(p.logits);
+  const int cc = min(CC, p.C - c0), nv = cc >> 3, hg = cc / R, h0 = c0 / R;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  for (int i = threadIdx.x; i < rows * nv; i += kThreads) {
+    const int r = i / nv, vc = i - r * nv;
+    float v[8];
+    const int ts = t0 - KM + r;
+    if (ts >= 0) {
+      load8(x + (static_cast<long>(ts) * B + b) * p.ldx + c0 + vc * 8, v);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) xs[r * CCP + vc * 8 + j] = v[j];
+    const int tf = t0 + r;
+    if (tf < p.T) {
+      load8(dy + (static_cast<long>(tf) * B + b) * p.lddy + c0 + vc * 8, v);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dys[r * CCP + vc * 8 + j] = v[j];
+  }
+  for (int i = warp; i < rows * hg; i += kThreads / 32) {
+    const int r = i / hg, hl = i - r * hg;
+    float* o = taps + (r * HG + hl) * K;
+    if (t0 + r < p.T) {
+      warp_softmax_taps(lg + (static_cast<long>(t0 + r) * B + b) * p.ldl + (h0 + hl) * K, K, o, lane);
+    } else {
+      for (int j = lane; j < K; j += 32) o[j] = 0.f;
+    }
+  }
+  __syncthreads();
+
+  // dx[ts] = sum_j w[ts+KM-j][j] * dy[ts+KM-j]   (value path)
+  T* dx = reinterpret_cast<T*>(p.dx);
+  for (int i = threadIdx.x; i < TT * nv; i += kThreads) {
+    const int t = i / nv, vc = i - t * nv;
+    const int hl = (vc * 8) / R;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int j = 0; j < K; ++j) {
+      const int r = t + KM - j;                     // local row of the consuming timestep
+      const float wj = taps[(r * HG + hl) * K + j];
+      const float* d = dys + r * CCP + vc * 8;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] = fmaf(wj, d[e], acc[e]);
+    }
+    store8(dx + (static_cast<long>(t0 + t) * B + b) * p.lddx + c0 + vc * 8, acc);
+  }
+  // dw[t][h][j] = sum_r dy[t][hR+r] * x[t-KM+j][hR+r] : one warp per (t, head), one lane per tap
+  for (int i = warp; i < TT * hg; i += kThreads / 32) {
+    const int t = i / hg, hl = i - t * hg;
+    for (int jb = 0; jb < K; jb += 32) {
+      const int j = jb + lane;
+      float s = 0.f;
+      if (j < K) {
+        const float* xr = xs + (t + j) * CCP + hl * R;     // local row of input t-KM+j is t+j
+        const float* d = dys + t * CCP + hl * R;
+        for (int r = 0; r < R; ++r) s = fmaf(d[r], xr[r], s);
+        dws[(t * HG + hl) * K + j] = s;
+      }
+    }
+    __syncwarp();
+    // softmax backward: dl_j = w_j * (dw_j - sum_i w_i dw_i)
+    const float* w = taps + (t * HG + hl) * K;
+    const float* dwp = dws + (t * HG + hl) * K;
+    float dot = 0.f;
+    for (int j = lane; j < K; j += 32) dot = fmaf(w[j], dwp[j], dot);
+    dot = warp_sum(dot);
+    T* dl = reinterpret_cast<T*>(p.dlogits) + (static_cast<long>(t0 + t) * B + b) * p.lddl + (h0 + hl) * K;
+    for (int j = lane; j < K; j += 32) dl[j] = from_f<T>(w[j] * (dwp[j] - dot));
+  }
+}
+
+int pick_group(int C, int H, int target, int* CC, int* HG) {
+  const int R = C / H;
+  int hg = target / R;
+  if (hg < 1) hg = 1;
+  if (hg > H) hg = H;
+  *HG = hg;
+  *CC = hg * R;
+  return (H + hg - 1) / hg;
+}
+
+template <typename K>
+int set_smem(K kern, size_t bytes) {
+  if (bytes > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes));
+    if (e != cudaSuccess) {
+      set_error("dynconv: %zu bytes of shared memory unavailable (%s)", bytes, cudaGetErrorString(e));
+      return TNT_ERR_CUDA;
+    }
+  }
+  return TNT_OK;
+}
+}  // namespace
+
+static int check_common(const void* x, long ldx, int T, int B, int C, int H, int K, int dtype) {
+  TNT_CHECK_ARG(x && T >= 0 && B > 0 && C > 0 && H > 0 && K > 0, "dynconv: bad arguments");
+  TNT_CHECK_ARG(C % H == 0 && (C / H) % 8 == 0, "dynconv: channels per head (%d/%d) must be a multiple of 8", C, H);
+  TNT_CHECK_ARG(dtype == TNT_F32 || dtype == TNT_BF16, "dynconv: dtype");
+  TNT_CHECK_ALIGN(aligned16(x) && ldx % 8 == 0, "dynconv: x must be 16-byte aligned, ldx %% 8 == 0");
+  return TNT_OK;
+}
+
+}  // namespace tnt
+
+extern "C" int tnt_dynconv_fwd(const tnt_dynconv_params* p, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(p, "dynconv: null params");
+  TNT_TRY(check_common(p->x, p->ldx, p->T, p->B, p->C, p->H, p->K, p->dtype));
+  TNT_CHECK_ARG(p->logits && p->y, "dynconv: null logits / y");
+  TNT_CHECK_ALIGN(aligned16(p->y) && p->ldy % 8 == 0, "dynconv: y alignment");
+  TNT_CHECK_ARG(!p->hist || p->hist_len <= p->K - 1, "dynconv: hist_len > K-1");
+  if (p->T == 0) return TNT_OK;
+  int CC, HG;
+  const int ngroups = pick_group(p->C, p->H, 256, &CC, &HG);
+  const size_t smem = (static_cast<size_t>(kTT + p->K - 1) * CC + static_cast<size_t>(kTT) * HG * p->K) * 4;
+  dim3 grid(p->B, ngroups, (p->T + kTT - 1) / kTT);
+  if (p->dtype == TNT_BF16) {
+    TNT_TRY(set_smem(dynconv_fwd_kernel<bf16>, smem));
+    dynconv_fwd_kernel<bf16><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG);
+  } else {
+    TNT_TRY(set_smem(dynconv_fwd_kernel<float>, smem));
+    dynconv_fwd_kernel<float><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG);
+  }
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+extern "C" int tnt_dynconv_step(const tnt_dynconv_step_params* p, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(p, "dynconv_step: null params");
+  TNT_TRY(check_common(p->x, p->ldx, 1, p->B, p->C, p->H, p->K, p->dtype));
+  TNT_CHECK_ARG(p->logits && p->y && (p->ring || p->K == 1), "dynconv_step: null logits / y / ring");
+  const size_t smem = static_cast<size_t>(p->H) * p->K * 4;
+  if (p->dtype == TNT_BF16)
+    dynconv_step_kernel<bf16><<<p->B, kThreads, smem, as_stream(stream)>>>(*p);
+  else
+    dynconv_step_kernel<float><<<p->B, kThreads, smem, as_stream(stream)>>>(*p);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+extern "C" int tnt_dynconv_bwd(const tnt_dynconv_bwd_params* p, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(p, "dynconv_bwd: null params");
+  TNT_TRY(check_common(p->x, p->ldx, p->T, p->B, p->C, p->H, p->K, p->dtype));
+  TNT_CHECK_ARG(p->logits && p->dy && p->dx && p->dlogits, "dynconv_bwd: null pointer");
+  TNT_CHECK_ALIGN(aligned16(p->dy) && aligned16(p->dx) && p->lddy % 8 == 0 && p->lddx % 8 == 0,
+                  "dynconv_bwd: dy / dx alignment");
+  if (p->T == 0) return TNT_OK;
+  int CC, HG;
+  const int ngroups = pick_group(p->C, p->H, 128, &CC, &HG);
+  const int rows = kTT + p->K - 1;
+  const size_t smem = (2 * static_cast<size_t>(rows) * (CC + 1) + static_cast<size_t>(rows) * HG * p->K +
+                       static_cast<size_t>(kTT) * HG * p->K) * 4;
+  dim3 grid(p->B, ngroups, (p->T + kTT - 1) / kTT);
+  if (p->dtype == TNT_BF16) {
+    TNT_TRY(set_smem(dynconv_bwd_kernel<bf16>, smem));
+    dynconv_bwd_kernel<bf16><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG);
+  } else {
+    TNT_TRY(set_smem(dynconv_bwd_kernel<float>, smem));
+    dynconv_bwd_kernel<float><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG);
+  }
+  TNT_LAUNCHED();
+  return TNT_OK;
+}

@@ -1,0 +1,309 @@
+// HBM-bound glue kernels: LayerNorm (+backward), embedding gather, weight-norm fold, casts.
+// One warp per row, 128-bit loads, fp32 statistics.
+#include "common.cuh"
+
+namespace tnt {
+namespace {
+
+constexpr int kWarps = 8;
+
+// ------------------------------------------------------------------------------ LayerNorm fwd
+// nn.LayerNorm (decoder_flattened.py:245-268) and final* LayerNorm (transformer_v2.py:82-94).
+template <typename T, int MAXV>
+__global__ void __launch_bounds__(kWarps * 32) layernorm_fwd_kernel(tnt_layernorm_params p) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * kWarps + (threadIdx.x >> 5);
+  if (row >= p.rows) return;
+  const T* x = reinterpret_cast<const T*>(p.x) + static_cast<long>(row) * p.ldx;
+  const int nv = p.C >> 3;
+  float v[MAXV > 0 ? MAXV : 1][8];
+  float sum = 0.f;
+  if (MAXV > 0) {
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int vc = lane + i * 32;
+      if (vc < nv) {
+        load8(x + vc * 8, v[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sum += v[i][j];
+      }
+    }
+  } else {
+    for (int vc = lane; vc < nv; vc += 32) {
+      float t[8];
+      load8(x + vc * 8, t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sum += t[j];
+    }
+  }
+  const float mean = warp_sum(sum) / p.C;
+  float sq = 0.f;
+  if (MAXV > 0) {
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      if (lane + i * 32 < nv) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d = v[i][j] - mean;
+          sq = fmaf(d, d, sq);
+        }
+      }
+    }
+  } else {
+    for (int vc = lane; vc < nv; vc += 32) {
+      float t[8];
+      load8(x + vc * 8, t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = t[j] - mean;
+        sq = fmaf(d, d, sq);
+      }
+    }
+  }
+  sq = warp_sum(sq);
+  const float rstd = p.variant == 0 ? rsqrtf(sq / p.C + p.eps) : 1.f / (sqrtf(sq / (p.C - 1)) + p.eps);
+  long orow = row;
+  if (p.transpose_T > 0) {
+    const int t = row / p.transpose_B, b = row - t * p.transpose_B;
+    orow = static_cast<long>(b) * p.transpose_T + t;
+  }
+  T* y = reinterpret_cast<T*>(p.y) + orow * p.ldy;
+  const float* gm = p.gamma + static_cast<long>(p.groups > 1 ? row % p.groups : 0) * p.C;
+  const float* bt = p.beta + static_cast<long>(p.groups > 1 ? row % p.groups : 0) * p.C;
+  auto emit = [&](int vc, float (&t)[8]) {
+    float gg[8], bb[8], o[8];
+    load8(gm + vc * 8, gg);
+    load8(bt + vc * 8, bb);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = (t[j] - mean) * rstd * gg[j] + bb[j];
+    store8(y + vc * 8, o);
+  };
+  if (MAXV > 0) {
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i)
+      if (lane + i * 32 < nv) emit(lane + i * 32, v[i]);
+  } else {
+    for (int vc = lane; vc < nv; vc += 32) {
+      float t[8];
+      load8(x + vc * 8, t);
+      emit(vc, t);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------ LayerNorm bwd
+// dgamma/dbeta: per-thread partials over the block's rows -> one atomicAdd per (block, channel).
+template <typename T>
+__global__ void __launch_bounds__(kWarps * 32) layernorm_bwd_kernel(tnt_layernorm_bwd_params p) {
+  extern __shared__ float sm[];                        // [2][C] block partials
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nv = p.C >> 3;
+  for (int i = threadIdx.x; i < 2 * p.C; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  for (int row = blockIdx.x * kWarps + warp; row < p.rows; row += gridDim.x * kWarps) {
+    const T* x = reinterpret_cast<const T*>(p.x) + static_cast<long>(row) * p.ldx;
+    const T* dy = reinterpret_cast<const T*>(p.dy) + static_cast<long>(row) * p.lddy;
+    T* dx = reinterpret_cast<T*>(p.dx) + static_cast<long>(row) * p.lddx;
+    float sum = 0.f;
+    for (int vc = lane; vc < nv; vc += 32) {
+      float t[8];
+      load8(x + vc * 8, t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sum += t[j];
+    }
+    const float mean = warp_sum(sum) / p.C;
+    float sq = 0.f;
+    for (int vc = lane; vc < nv; vc += 32) {
+      float t[8];
+      load8(x + vc * 8, t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sq = fmaf(t[j] - mean, t[j] - mean, sq);
+    }
+    const float rstd = rsqrtf(warp_sum(sq) / p.C + p.eps);
+    float s1 = 0.f, s2 = 0.f;                          // sum(dxhat), sum(dxhat * xhat)
+    for (int vc = lane; vc < nv; vc += 32) {
+      float t[8], d[8], g[8];
+      load8(x + vc * 8, t);
+      load8(dy + vc * 8, d);
+      load8(p.gamma + vc * 8, g);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xh = (t[j] - mean) * rstd, dxh = d[j] * g[j];
+        s1 += dxh;
+        s2 = fmaf(dxh, xh, s2);
+        atomicAdd(&sm[vc * 8 + j], d[j] * xh);
+        atomicAdd(&sm[p.C + vc * 8 + j], d[j]);
+      }
+    }
+    s1 = warp_sum(s1) / p.C;
+    s2 = warp_sum(s2) / p.C;
+    for (int vc = lane; vc < nv; vc += 32) {
+      float t[8], d[8], g[8], o[8];
+      load8(x + vc * 8, t);
+      load8(dy + vc * 8, d);
+      load8(p.gamma + vc * 8, g);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xh = (t[j] - mean) * rstd;
+        o[j] = rstd * (d[j] * g[j] - s1 - xh * s2);
+      }
+      store8(dx + vc * 8, o);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < p.C; i += blockDim.x) {
+    atomicAdd(p.dgamma + i, sm[i]);
+    atomicAdd(p.dbeta + i, sm[p.C + i]);
+  }
+}
+
+// ------------------------------------------------------------------------------ embedding
+// adaptive.py:61-76 (pre-projected bands) + positional.py:167-211 + sum_text_field_embedder.py:117
+template <typename T>
+__global__ void __launch_bounds__(kWarps * 32) embed_kernel(tnt_embed_params p) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * kWarps + (threadIdx.x >> 5);      // row = t * B + b
+  if (row >= p.T * p.B) return;
+  const int t = row / p.B, b = row - t * p.B;
+  const long id = p.ids[static_cast<long>(b) * p.T + t];
+  const int start = p.start_pos ? *p.start_pos : 0;
+  int pos = (id == p.pad_idx) ? p.pad_idx : t + p.pad_idx + 1 + start;
+  pos = min(pos, p.n_pos - 1);
+  const T* e = reinterpret_cast<const T*>(p.table) + id * p.d;
+  const float* pe = p.pos_table + static_cast<long>(pos) * p.d;
+  T* o = reinterpret_cast<T*>(p.out) + static_cast<long>(row) * p.ldo;
+  for (int vc = lane; vc < (p.d >> 3); vc += 32) {
+    float a[8], c[8];
+    load8(e + vc * 8, a);
+    load8(pe + vc * 8, c);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] += c[j];
+    store8(o + vc * 8, a);
+  }
+}
+
+// ------------------------------------------------------------------------------ weight-norm fold
+// w = g * v / ||v||_row  (linear.py:30-33); optional GLU pair interleave of the output rows.
+template <typename T>
+__global__ void __launch_bounds__(kWarps * 32) wn_fold_kernel(const float* v, const float* g, T* out, int rows,
+                                                              int cols, int glu) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * kWarps + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const float* vr = v + static_cast<long>(row) * cols;
+  float scale = 1.f;
+  if (g) {
+    float sq = 0.f;
+    for (int c = lane; c < cols; c += 32) sq = fmaf(vr[c], vr[c], sq);
+    scale = g[row] / sqrtf(warp_sum(sq));
+  }
+  int orow = row;
+  if (glu) orow = row < rows / 2 ? 2 * row : 2 * (row - rows / 2) + 1;
+  T* o = out + static_cast<long>(orow) * cols;
+  for (int c = lane; c < cols; c += 32) o[c] = from_f<T>(vr[c] * scale);
+}
+
+__global__ void glu_bias_kernel(const float* b, float* out, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i < n / 2 ? 2 * i : 2 * (i - n / 2) + 1] = b[i];
+}
+
+template <typename S, typename D>
+__global__ void cast_kernel(const S* s, D* d, long n) {
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long>(gridDim.x) * blockDim.x)
+    d[i] = from_f<D>(to_f(s[i]));
+}
+
+}  // namespace
+}  // namespace tnt
+
+extern "C" int tnt_layernorm_fwd(const tnt_layernorm_params* p, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(p && p->x && p->y && p->gamma && p->beta, "layernorm: null pointer");
+  TNT_CHECK_ARG(p->rows >= 0 && p->C > 1 && p->C % 8 == 0, "layernorm: C (%d) must be a multiple of 8", p->C);
+  TNT_CHECK_ALIGN(aligned16(p->x) && aligned16(p->y) && p->ldx % 8 == 0 && p->ldy % 8 == 0, "layernorm: alignment");
+  if (p->rows == 0) return TNT_OK;
+  const int grid = (p->rows + kWarps - 1) / kWarps;
+  cudaStream_t st = as_stream(stream);
+  const bool small = p->C <= 1024;
+  if (p->dtype == TNT_BF16) {
+    if (small) layernorm_fwd_kernel<bf16, 4><<<grid, kWarps * 32, 0, st>>>(*p);
+    else layernorm_fwd_kernel<bf16, 0><<<grid, kWarps * 32, 0, st>>>(*p);
+  } else {
+    if (small) layernorm_fwd_kernel<float, 4><<<grid, kWarps * 32, 0, st>>>(*p);
+    else layernorm_fwd_kernel<float, 0><<<grid, kWarps * 32, 0, st>>>(*p);
+  }
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+extern "C" int tnt_layernorm_bwd(const tnt_layernorm_bwd_params* p, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(p && p->x && p->dy && p->dx && p->gamma && p->dgamma && p->dbeta, "layernorm_bwd: null pointer");
+  TNT_CHECK_ARG(p->C % 8 == 0 && p->C <= 6000, "layernorm_bwd: C");
+  if (p->rows == 0) return TNT_OK;
+  const int grid = std::min((p->rows + kWarps - 1) / kWarps, 2 * num_sms());
+  const size_t smem = 2 * static_cast<size_t>(p->C) * 4;
+  if (p->dtype == TNT_BF16)
+    layernorm_bwd_kernel<bf16><<<grid, kWarps * 32, smem, as_stream(stream)>>>(*p);
+  else
+    layernorm_bwd_kernel<float><<<grid, kWarps * 32, smem, as_stream(stream)>>>(*p);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+extern "C" int tnt_embed_fwd(const tnt_embed_params* p, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(p && p->ids && p->table && p->pos_table && p->out, "embed: null pointer");
+  TNT_CHECK_ARG(p->d % 8 == 0 && p->ldo % 8 == 0, "embed: d must be a multiple of 8");
+  const int rows = p->B * p->T;
+  if (rows == 0) return TNT_OK;
+  const int grid = (rows + kWarps - 1) / kWarps;
+  if (p->dtype == TNT_BF16) embed_kernel<bf16><<<grid, kWarps * 32, 0, as_stream(stream)>>>(*p);
+  else embed_kernel<float><<<grid, kWarps * 32, 0, as_stream(stream)>>>(*p);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+extern "C" int tnt_wn_fold(const float* v, const float* g, void* w_out, int rows, int cols, int glu_interleave,
+                           int dtype_out, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(v && w_out && rows > 0 && cols > 0, "wn_fold: bad arguments");
+  TNT_CHECK_ARG(!glu_interleave || rows % 2 == 0, "wn_fold: GLU interleave needs an even row count");
+  const int grid = (rows + kWarps - 1) / kWarps;
+  if (dtype_out == TNT_BF16)
+    wn_fold_kernel<bf16><<<grid, kWarps * 32, 0, as_stream(stream)>>>(v, g, reinterpret_cast<bf16*>(w_out), rows, cols,
+                                                                      glu_interleave);
+  else
+    wn_fold_kernel<float><<<grid, kWarps * 32, 0, as_stream(stream)>>>(v, g, reinterpret_cast<float*>(w_out), rows,
+                                                                       cols, glu_interleave);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+extern "C" int tnt_glu_interleave_bias(const float* b, float* b_out, int n, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(b && b_out && n > 0 && n % 2 == 0, "glu_interleave_bias: bad arguments");
+  glu_bias_kernel<<<(n + 255) / 256, 256, 0, as_stream(stream)>>>(b, b_out, n);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+extern "C" int tnt_cast(const void* src, void* dst, int64_t n, int dtype_src, int dtype_dst, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(src && dst && n >= 0, "cast: bad arguments");
+  if (n == 0) return TNT_OK;
+  const int grid = static_cast<int>(std::min<int64_t>((n + 255) / 256, 148 * 16));
+  cudaStream_t st = as_stream(stream);
+  if (dtype_src == TNT_F32 && dtype_dst == TNT_BF16)
+    cast_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float*>(src), reinterpret_cast<bf16*>(dst), n);
+  else if (dtype_src == TNT_BF16 && dtype_dst == TNT_F32)
+    cast_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const bf16*>(src), reinterpret_cast<float*>(dst), n);
+  else if (dtype_src == TNT_F32 && dtype_dst == TNT_F32)
+    cast_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float*>(src), reinterpret_cast<float*>(dst), n);
+  else
+    cast_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const bf16*>(src), reinterpret_cast<bf16*>(dst), n);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}

@@ -1,0 +1,82 @@
+// Decoder engine state: prepared weights (weight-norm folded, fused per-source projections, engine
+// dtype) and the workspace layouts.  See engine_load.cu / engine_fwd.cu.
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+
+#include "adasoftmax.cuh"
+
+namespace tnt {
+
+struct RawTensor {
+  const float* data;
+  std::vector<int64_t> shape;
+  int64_t numel() const {
+    int64_t n = 1;
+    for (auto s : shape) n *= s;
+    return n;
+  }
+};
+
+struct LayerW {
+  int K;
+  void* w1; float* b1;            // [2d, d] GLU pair-interleaved, bias likewise
+  void* wtap;                     // [H*K, d]
+  void* w2; float* b2;            // [d, d]
+  float* ln_conv_g; float* ln_conv_b;
+  void* wq; float* bq;            // [n_src*d, d]: the query projections of all sources stacked
+  void* wo; float* bo;            // [n_src][d, d], [n_src*d]
+  float* bias_k; float* bias_v;   // [n_src*d]
+  float* ln_src_g; float* ln_src_b;   // [n_src, d]
+  void* wc; float* bc;            // [d, n_src*d]
+  void* wf1; float* bf1;          // [ffn, d]
+  void* wf2; float* bf2;          // [d, ffn]
+  float* ln_f_g; float* ln_f_b;
+};
+
+}  // namespace tnt
+
+struct tnt_decoder {
+  tnt_decoder_config cfg;
+  std::map<std::string, tnt::RawTensor> raw;
+  bool finalized = false;
+  char* wmem = nullptr;
+  size_t wbytes = 0;
+  // prepared weights
+  std::vector<tnt::LayerW> layers;
+  void* wkv[TNT_MAX_SOURCES] = {};     // [L*2d, source_dim]: per layer K rows then V rows
+  float* bkv[TNT_MAX_SOURCES] = {};    // [L*2d]
+  void* table = nullptr;               // [vocab, d] pre-projected, pre-scaled embedding
+  float* pos_table = nullptr;          // [max_positions, d]
+  tnt::AdaSoftmax ada;
+  void* scratch_dd = nullptr;          // [d, d] fp32 (finalize only)
+  int article_idx = -1;
+
+  int d() const { return cfg.d; }
+  int nsrc() const { return cfg.n_sources; }
+  size_t esz() const { return tnt::dtype_size(cfg.dtype); }
+  int ld_logits(int K) const { return (cfg.heads * K + 7) & ~7; }
+  int max_ld_logits() const {
+    int m = 0;
+    for (int l = 0; l < cfg.n_layers; ++l) m = std::max(m, ld_logits(cfg.kernels[l]));
+    return m;
+  }
+};
+
+namespace tnt {
+
+// forward workspace (teacher forcing and single-step share it; N = T*B rows)
+struct FwdWs {
+  void *X0, *X1, *h, *logits, *cbuf, *ybuf, *Q, *AO, *CAT, *F;
+  void* kv[TNT_MAX_SOURCES];
+  size_t total;
+};
+FwdWs carve_fwd(const tnt_decoder* d, int B, int T, const int* S, void* ws, bool with_kv);
+
+int project_kv(tnt_decoder* d, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st);
+// one decoder layer on N = T*B rows; `ring`/`pos` != NULL selects the single-step conv (T must be 1)
+int run_layer(tnt_decoder* d, int l, const tnt_contexts* ctx, const FwdWs& w, const void* Xin, void* Xout, int B, int T,
+              void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st);
+
+}  // namespace tnt

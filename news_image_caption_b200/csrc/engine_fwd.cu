@@ -1,0 +1,190 @@
+// Decoder engine: teacher-forced forward, loss / log-probs, greedy generation with incremental state.
+//   DynamicConvDecoder.forward       ttl/tell/models/decoder_flattened.py:96-146
+//   DynamicConvDecoderLayer.forward  ttl/tell/models/decoder_flattened.py:271-345 (post-LN),
+//                                    ttl/tell/models/decoder_faces_objects.py:283-393
+//   _generate (top-1)                ttl/tell/models/transformer_flattened.py:238-325
+#include "engine.cuh"
+
+namespace tnt {
+
+int xattn_check(const tnt_xattn_params* p);
+int xattn_fwd_dispatch(const tnt_xattn_params* p, cudaStream_t st);
+
+namespace {
+inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
+
+int linear(const void* a, long lda, const void* w, long ldw, const float* bias, void* c, long ldc, int M, int N, int K,
+           int dtype, int epi, const void* res, long ldr, cudaStream_t st, int groups = 1, long sa = 0, long sw = 0,
+           long sb = 0, long sr = 0, long sc = 0) {
+  tnt_linear_params p = {};
+  p.a = a; p.lda = lda; p.w = w; p.ldw = ldw; p.bias = bias; p.residual = res; p.ldr = ldr; p.c = c; p.ldc = ldc;
+  p.M = M; p.N = N; p.K = K; p.groups = groups;
+  p.stride_a = sa; p.stride_w = sw; p.stride_bias = sb; p.stride_res = sr; p.stride_c = sc;
+  p.dtype_in = dtype; p.dtype_out = dtype; p.epilogue = epi;
+  return launch_gemm(&p, -1, nullptr, nullptr, st);
+}
+
+int layernorm(const void* x, void* y, long ld, const float* g, const float* b, int rows, int C, int groups, int dtype,
+              int tT, int tB, cudaStream_t st) {
+  tnt_layernorm_params p = {};
+  p.x = x; p.ldx = ld; p.y = y; p.ldy = ld; p.gamma = g; p.beta = b;
+  p.rows = rows; p.C = C; p.groups = groups; p.variant = 0; p.eps = 1e-5f; p.dtype = dtype;
+  p.transpose_T = tT; p.transpose_B = tB;
+  return tnt_layernorm_fwd(&p, st);
+}
+}  // namespace
+
+FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool with_kv) {
+  const tnt_decoder_config& c = D->cfg;
+  const size_t E = D->esz(), N = static_cast<size_t>(B) * T, d = c.d, ns = c.n_sources;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = ws ? static_cast<char*>(ws) + off : nullptr;
+    off += al256(bytes);
+    return p;
+  };
+  FwdWs w;
+  w.X0 = take(N * d * E); w.X1 = take(N * d * E); w.h = take(N * d * E);
+  w.logits = take(N * D->max_ld_logits() * E);
+  w.cbuf = take(N * d * E); w.ybuf = take(N * d * E);
+  w.Q = take(N * ns * d * E); w.AO = take(N * ns * d * E); w.CAT = take(N * ns * d * E);
+  w.F = take(N * c.ffn * E);
+  for (size_t s = 0; s < ns; ++s)
+    w.kv[s] = with_kv ? take(static_cast<size_t>(S[s]) * B * c.n_layers * 2 * d * E) : nullptr;
+  w.total = off;
+  return w;
+}
+
+// K/V of every layer for every source in ONE GEMM per source: [S*B, kdim] x [L*2d, kdim]^T (+bias).
+// The reference recomputes these projections in every layer call and every decoding step
+// (multi_head.py:347-352 with incremental_state=None, decoder_flattened.py:305,323); same numbers.
+int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st) {
+  const tnt_decoder_config& c = D->cfg;
+  const int ldkv = c.n_layers * 2 * c.d;
+  for (int s = 0; s < c.n_sources; ++s) {
+    if (ctx->S[s] == 0) continue;
+    TNT_CHECK_ARG(ctx->memory[s], "decoder: context '%s' missing", c.source_names[s]);
+    TNT_TRY(linear(ctx->memory[s], c.source_dim[s], D->wkv[s], c.source_dim[s], D->bkv[s], w.kv[s], ldkv,
+                   ctx->S[s] * ctx->B, ldkv, c.source_dim[s], c.dtype, EPI_NONE, nullptr, 0, st));
+  }
+  return TNT_OK;
+}
+
+int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, const void* Xin, void* Xout, int B, int T,
+              void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st) {
+  const tnt_decoder_config& c = D->cfg;
+  const LayerW& L = D->layers[l];
+  const int d = c.d, ns = c.n_sources, N = B * T, H = c.heads, dt = c.dtype;
+  const int ldl = D->ld_logits(L.K);
+  const size_t E = D->esz();
+  // conv block: linear1 + GLU -> tap logits -> dynamic conv -> linear2 + residual -> LayerNorm
+  TNT_TRY(linear(Xin, d, L.w1, d, L.b1, w.h, d, N, 2 * d, d, dt, EPI_GLU, nullptr, 0, st));
+  TNT_TRY(linear(w.h, d, L.wtap, d, nullptr, w.logits, ldl, N, H * L.K, d, dt, EPI_NONE, nullptr, 0, st));
+  if (ring || pos) {
+    TNT_CHECK_ARG(T == 1, "decoder: incremental layer call needs T == 1");
+    tnt_dynconv_step_params sp = {};
+    sp.x = w.h; sp.ldx = d; sp.logits = w.logits; sp.ldl = ldl; sp.y = w.cbuf; sp.ldy = d; sp.ring = ring; sp.pos = pos;
+    sp.B = B; sp.C = d; sp.H = H; sp.K = L.K; sp.dtype = dt;
+    TNT_TRY(tnt_dynconv_step(&sp, st));
+  } else {
+    tnt_dynconv_params cp = {};
+    cp.x = w.h; cp.ldx = d; cp.logits = w.logits; cp.ldl = ldl; cp.y = w.cbuf; cp.ldy = d;
+    cp.T = T; cp.B = B; cp.C = d; cp.H = H; cp.K = L.K; cp.dtype = dt;
+    TNT_TRY(tnt_dynconv_fwd(&cp, st));
+  }
+  TNT_TRY(linear(w.cbuf, d, L.w2, d, L.b2, w.ybuf, d, N, d, d, dt, EPI_RESIDUAL, Xin, d, st));
+  TNT_TRY(layernorm(w.ybuf, w.X1, d, L.ln_conv_g, L.ln_conv_b, N, d, 1, dt, 0, 0, st));
+  // multi-source cross attention: one stacked query projection, per-source attention, grouped out-proj
+  TNT_TRY(linear(w.X1, d, L.wq, d, L.bq, w.Q, static_cast<long>(ns) * d, N, ns * d, d, dt, EPI_NONE, nullptr, 0, st));
+  const long ldkv = static_cast<long>(c.n_layers) * 2 * d;
+  for (int s = 0; s < ns; ++s) {
+    tnt_xattn_params ap = {};
+    ap.q = static_cast<const char*>(w.Q) + static_cast<size_t>(s) * d * E;
+    ap.q_stride_t = static_cast<long>(B) * ns * d; ap.q_stride_b = static_cast<long>(ns) * d;
+    ap.k = static_cast<const char*>(w.kv[s]) + static_cast<size_t>(l) * 2 * d * E;
+    ap.k_stride_s = static_cast<long>(B) * ldkv; ap.k_stride_b = ldkv;
+    ap.v = static_cast<const char*>(ap.k) + static_cast<size_t>(d) * E;
+    ap.v_stride_s = ap.k_stride_s; ap.v_stride_b = ap.k_stride_b;
+    ap.out = static_cast<char*>(w.AO) + static_cast<size_t>(s) * d * E;
+    ap.o_stride_t = ap.q_stride_t; ap.o_stride_b = ap.q_stride_b;
+    ap.mask = ctx->pad_mask[s]; ap.m_stride_b = ctx->S[s]; ap.m_stride_t = 0;
+    ap.mask_mode = (ctx->pad_mask[s] && ctx->S[s] > 0) ? TNT_MASK_KEY_PADDING : TNT_MASK_NONE;
+    ap.bias_k = L.bias_k + s * d; ap.bias_v = L.bias_v + s * d;
+    ap.weights = (attn_out && s == D->article_idx) ? attn_out : nullptr;
+    ap.B = B; ap.T = T; ap.S = ctx->S[s]; ap.H = H; ap.D = d / H; ap.n_extra = 2;
+    ap.scale = 1.0f / sqrtf(static_cast<float>(d / H));
+    ap.dtype = dt;
+    if (ap.S == 0) { ap.k = ap.q; ap.v = ap.q; }           // no memory rows: only the 2 extra keys
+    TNT_TRY(xattn_check(&ap));
+    TNT_TRY(xattn_fwd_dispatch(&ap, st));
+  }
+  TNT_TRY(linear(w.AO, static_cast<long>(ns) * d, L.wo, d, L.bo, w.CAT, static_cast<long>(ns) * d, N, d, d, dt, EPI_RESIDUAL,
+                 w.X1, d, st, ns, d, static_cast<long>(d) * d, d, 0, d));
+  TNT_TRY(layernorm(w.CAT, w.CAT, d, L.ln_src_g, L.ln_src_b, N * ns, d, ns, dt, 0, 0, st));
+  TNT_TRY(linear(w.CAT, static_cast<long>(ns) * d, L.wc, static_cast<long>(ns) * d, L.bc, w.X0, d, N, d, ns * d, dt, EPI_NONE,
+                 nullptr, 0, st));
+  // feed-forward
+  TNT_TRY(linear(w.X0, d, L.wf1, d, L.bf1, w.F, c.ffn, N, c.ffn, d, dt, EPI_RELU, nullptr, 0, st));
+  TNT_TRY(linear(w.F, c.ffn, L.wf2, c.ffn, L.bf2, w.ybuf, d, N, d, c.ffn, dt, EPI_RESIDUAL, w.X0, d, st));
+  TNT_TRY(layernorm(w.ybuf, Xout, d, L.ln_f_g, L.ln_f_b, N, d, 1, dt, transpose_out ? T : 0, transpose_out ? B : 0, st));
+  return TNT_OK;
+}
+
+static int embed(tnt_decoder* D, const int64_t* ids, int B, int T, void* out, const int* start_pos, cudaStream_t st) {
+  tnt_embed_params e = {};
+  e.ids = ids; e.table = D->table; e.pos_table = D->pos_table; e.out = out; e.ldo = D->cfg.d; e.start_pos = start_pos;
+  e.B = B; e.T = T; e.d = D->cfg.d; e.n_pos = D->cfg.max_positions; e.pad_idx = D->cfg.pad_idx; e.dtype = D->cfg.dtype;
+  return tnt_embed_fwd(&e, st);
+}
+
+}  // namespace tnt
+
+using namespace tnt;
+
+extern "C" size_t tnt_decoder_workspace_bytes(const tnt_decoder* d, int B, int T, const int* S) {
+  if (!d || !S) return 0;
+  return carve_fwd(d, B, T, S, nullptr, true).total;
+}
+
+extern "C" int tnt_decoder_forward(tnt_decoder* D, const int64_t* ids, const tnt_contexts* ctx, void* X_out,
+                                   float* attn_out, void* workspace, size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized, "decoder_forward: decoder not finalized");
+  TNT_CHECK_ARG(ids && ctx && X_out && workspace, "decoder_forward: null pointer");
+  const int B = ctx->B, T = ctx->T;
+  TNT_CHECK_ARG(B > 0 && T > 0, "decoder_forward: empty batch");
+  TNT_CHECK_ARG(T + D->cfg.pad_idx + 1 <= D->cfg.max_positions, "decoder_forward: T=%d exceeds the position table", T);
+  TNT_CHECK_ALIGN((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "decoder_forward: workspace alignment");
+  FwdWs w = carve_fwd(D, B, T, ctx->S, workspace, true);
+  if (w.total > workspace_bytes) {
+    set_error("decoder_forward: workspace %zu < %zu", workspace_bytes, w.total);
+    return TNT_ERR_WORKSPACE;
+  }
+  cudaStream_t st = as_stream(stream);
+  TNT_TRY(project_kv(D, ctx, w, st));
+  TNT_TRY(embed(D, ids, B, T, w.X0, nullptr, st));
+  // layer input lives in X0; run_layer uses X0/X1 internally, so ping-pong through cbuf-sized buffers:
+  // layer l reads `cur` and writes `nxt`; both are distinct from the internals (X0 is consumed first).
+  const int Ls = D->cfg.n_layers;
+  void* cur = w.X0;
+  for (int l = 0; l < Ls; ++l) {
+    const bool last = l == Ls - 1;
+    // Xin == w.X0 is safe: X0 is only overwritten by context_fc after its last use as residual.
+    void* out = last ? X_out : w.X0;
+    TNT_TRY(run_layer(D, l, ctx, w, cur, out, B, T, nullptr, nullptr, last ? attn_out : nullptr, last, st));
+    cur = out;
+  }
+  return TNT_OK;
+}
+
+extern "C" int tnt_decoder_nll(tnt_decoder* D, const void* X, const int64_t* target, int n_rows, float* out2,
+                               void* workspace, size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized && X && target && out2 && workspace, "decoder_nll: bad arguments");
+  return adasoftmax_nll(D->ada, X, D->cfg.d, target, n_rows, D->cfg.pad_idx, out2, workspace, workspace_bytes,
+                        as_stream(stream));
+}
+
+extern "C" int tnt_decoder_log_prob(tnt_decoder* D, const void* X, int n_rows, float* out, void* workspace,
+                                    size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized && X && out && workspace, "decoder_log_prob: bad arguments");
+  return adasoftmax_logprob(D->ada, X, D->cfg.d, n_rows, out, workspace, workspace_bytes, as_stream(stream));
+}

@@ -1,0 +1,245 @@
+// Decoder engine: greedy generation with incremental DynamicConv ring buffers + cached K/V (kernel
+// group 5), and the host-buffer scoring entry used for the end-to-end benchmark.
+//   _generate (sampling_topk=1)  ttl/tell/models/transformer_flattened.py:238-325,
+//                                ttl/tell/models/transformer_faces_objects.py:399-494
+//   incremental conv buffer      ttl/tell/modules/convolutions/dynamic.py:95-99,114-116,338-348
+//   incremental positions        ttl/tell/modules/token_embedders/positional.py:170-174,198-199
+// Differences in mechanism, not in numbers: finished rows stay in the batch (masked) instead of being
+// compacted away every step, K/V projections are computed once instead of once per step and layer,
+// and steps 1.. are replayed from one captured CUDA graph (the step counter lives on the device).
+#include "engine.cuh"
+
+namespace tnt {
+
+namespace {
+inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
+
+struct GenWs {
+  FwdWs f;
+  void* ring[TNT_MAX_LAYERS];
+  int* pos; int* done_step; uint8_t* active; int64_t* cur; int64_t* tok; float* logp; void* ada;
+  size_t ada_bytes, total;
+};
+
+GenWs carve_gen(const tnt_decoder* D, int B, const int* S, void* ws) {
+  GenWs g;
+  g.f = carve_fwd(D, B, 1, S, ws, true);
+  size_t off = g.f.total;
+  auto take = [&](size_t bytes) {
+    void* p = ws ? static_cast<char*>(ws) + off : nullptr;
+    off += al256(bytes);
+    return p;
+  };
+  for (int l = 0; l < D->cfg.n_layers; ++l)
+    g.ring[l] = take(static_cast<size_t>(std::max(D->cfg.kernels[l] - 1, 1)) * B * D->cfg.d * D->esz());
+  g.pos = static_cast<int*>(take(2 * sizeof(int)));
+  g.done_step = g.pos + 1;
+  g.active = static_cast<uint8_t*>(take(B));
+  g.cur = static_cast<int64_t*>(take(sizeof(int64_t) * B));
+  g.tok = static_cast<int64_t*>(take(sizeof(int64_t) * B));
+  g.logp = static_cast<float*>(take(sizeof(float) * B));
+  g.ada_bytes = adasoftmax_workspace_bytes(D->ada, B, false);
+  g.ada = take(g.ada_bytes);
+  g.total = off;
+  return g;
+}
+
+__global__ void gen_init_kernel(const int64_t* seed, int B, int L, int eos, int64_t* cur, uint8_t* active, int64_t* ids_out,
+                                int* pos) {
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    cur[b] = seed[b];
+    active[b] = seed[b] != eos;
+    ids_out[static_cast<long>(b) * (L + 1)] = seed[b];
+  }
+  if (threadIdx.x == 0) {
+    pos[0] = 0;
+    pos[1] = -1;
+  }
+}
+
+// scatter this step's tokens / log-probs, retire rows that produced EOS (transformer_flattened.py:290-313)
+__global__ void __launch_bounds__(1024) gen_update_kernel(const int64_t* tok, const float* logp, int B, int L, int eos,
+                                                          int pad, int64_t* cur, uint8_t* active, int64_t* ids_out,
+                                                          float* logp_out, int* pos) {
+  __shared__ int any_active;
+  const int step = pos[0];
+  if (threadIdx.x == 0) any_active = 0;
+  __syncthreads();
+  if (step < L) {
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+      const int64_t t = tok[b];
+      if (active[b]) {
+        ids_out[static_cast<long>(b) * (L + 1) + step + 1] = t;
+        logp_out[static_cast<long>(b) * L + step] = logp[b];
+        if (t == eos) active[b] = 0;
+        else any_active = 1;
+      } else {
+        ids_out[static_cast<long>(b) * (L + 1) + step + 1] = pad;
+        logp_out[static_cast<long>(b) * L + step] = 0.f;
+      }
+      cur[b] = t;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    pos[0] = step + 1;
+    if (!any_active && pos[1] < 0) pos[1] = step + 1;
+  }
+}
+
+int gen_step(tnt_decoder* D, const tnt_contexts* ctx1, const GenWs& g, int B, int L, int eos, int64_t* ids_out,
+             float* logp_out, cudaStream_t st) {
+  tnt_embed_params e = {};
+  e.ids = g.cur; e.table = D->table; e.pos_table = D->pos_table; e.out = g.f.X0; e.ldo = D->cfg.d; e.start_pos = g.pos;
+  e.B = B; e.T = 1; e.d = D->cfg.d; e.n_pos = D->cfg.max_positions; e.pad_idx = D->cfg.pad_idx; e.dtype = D->cfg.dtype;
+  TNT_TRY(tnt_embed_fwd(&e, st));
+  for (int l = 0; l < D->cfg.n_layers; ++l)
+    TNT_TRY(run_layer(D, l, ctx1, g.f, g.f.X0, g.f.X0, B, 1, g.ring[l], g.pos, nullptr, false, st));
+  TNT_TRY(adasoftmax_greedy(D->ada, g.f.X0, D->cfg.d, B, g.tok, g.logp, g.ada, g.ada_bytes, st));
+  gen_update_kernel<<<1, 1024, 0, st>>>(g.tok, g.logp, B, L, eos, D->cfg.pad_idx, g.cur, g.active, ids_out, logp_out, g.pos);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+}  // namespace
+}  // namespace tnt
+
+using namespace tnt;
+
+extern "C" size_t tnt_decoder_generate_workspace_bytes(const tnt_decoder* d, int B, int gen_len, const int* S) {
+  (void)gen_len;
+  if (!d || !S) return 0;
+  return carve_gen(d, B, S, nullptr).total;
+}
+
+extern "C" int tnt_decoder_generate(tnt_decoder* D, const int64_t* seed, const tnt_contexts* ctx, int gen_len, int eos,
+                                    int64_t* ids_out, float* logp_out, int* steps_host, void* workspace,
+                                    size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized, "decoder_generate: decoder not finalized");
+  TNT_CHECK_ARG(seed && ctx && ids_out && logp_out && workspace && gen_len > 0, "decoder_generate: bad arguments");
+  const int B = ctx->B;
+  TNT_CHECK_ARG(gen_len + D->cfg.pad_idx + 1 <= D->cfg.max_positions, "decoder_generate: gen_len exceeds the position table");
+  GenWs g = carve_gen(D, B, ctx->S, workspace);
+  if (g.total > workspace_bytes) {
+    set_error("decoder_generate: workspace %zu < %zu", workspace_bytes, g.total);
+    return TNT_ERR_WORKSPACE;
+  }
+  cudaStream_t st = as_stream(stream);
+  tnt_contexts c1 = *ctx;
+  c1.T = 1;
+  gen_init_kernel<<<1, 1024, 0, st>>>(seed, B, gen_len, eos, g.cur, g.active, ids_out, g.pos);
+  TNT_LAUNCHED();
+  TNT_TRY(project_kv(D, &c1, g.f, st));
+  TNT_TRY(gen_step(D, &c1, g, B, gen_len, eos, ids_out, logp_out, st));          // step 0 eagerly
+  if (gen_len > 1) {
+    // steps 1.. : capture ONE step on a private stream (the caller's may be the legacy stream, which
+    // cannot be captured) and replay it on the caller's stream.
+    cudaStream_t cs;
+    TNT_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    int rc = TNT_OK;
+    cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
+    const uint64_t n0 = tnt_launch_count();
+    if (e == cudaSuccess) {
+      rc = gen_step(D, &c1, g, B, gen_len, eos, ids_out, logp_out, cs);
+      e = cudaStreamEndCapture(cs, &graph);
+    }
+    const int per_step = static_cast<int>(tnt_launch_count() - n0);   // kernels recorded in the graph
+    if (rc == TNT_OK && e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
+    if (rc == TNT_OK && e == cudaSuccess) {
+      for (int i = 1; i < gen_len && e == cudaSuccess; ++i) e = cudaGraphLaunch(exec, st);
+      count_launch((gen_len - 2) * per_step);   // capture counted one step; gen_len-1 replays executed
+    }
+    if (exec) cudaGraphExecDestroy(exec);
+    if (graph) cudaGraphDestroy(graph);
+    cudaStreamDestroy(cs);
+    if (rc != TNT_OK) return rc;
+    if (e != cudaSuccess) {
+      set_error("decoder_generate: CUDA graph replay failed: %s", cudaGetErrorString(e));
+      return TNT_ERR_CUDA;
+    }
+  }
+  if (steps_host) {
+    int two[2];
+    TNT_CUDA(cudaMemcpyAsync(two, g.pos, sizeof(two), cudaMemcpyDeviceToHost, st));
+    TNT_CUDA(cudaStreamSynchronize(st));
+    *steps_host = two[1] < 0 ? gen_len : two[1];
+  }
+  return TNT_OK;
+}
+
+// ------------------------------------------------------------------------------ host-buffer scoring
+namespace tnt {
+namespace {
+struct Staging {
+  int64_t* ids; int64_t* tgt; void* mem[TNT_MAX_SOURCES]; uint8_t* mask[TNT_MAX_SOURCES]; void* X; float* out2;
+  size_t total;
+};
+Staging carve_staging(const tnt_decoder* D, int B, int T, const int* S, void* base) {
+  Staging s;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = base ? static_cast<char*>(base) + off : nullptr;
+    off += al256(bytes);
+    return p;
+  };
+  s.ids = static_cast<int64_t*>(take(sizeof(int64_t) * B * T));
+  s.tgt = static_cast<int64_t*>(take(sizeof(int64_t) * B * T));
+  for (int i = 0; i < D->cfg.n_sources; ++i) {
+    s.mem[i] = take(static_cast<size_t>(S[i]) * B * D->cfg.source_dim[i] * D->esz());
+    s.mask[i] = static_cast<uint8_t*>(take(static_cast<size_t>(S[i]) * B));
+  }
+  s.X = take(static_cast<size_t>(B) * T * D->cfg.d * D->esz());
+  s.out2 = static_cast<float*>(take(2 * sizeof(float)));
+  s.total = off;
+  return s;
+}
+}  // namespace
+}  // namespace tnt
+
+extern "C" size_t tnt_decoder_score_host_staging_bytes(const tnt_decoder* d, int B, int T, const int* S) {
+  if (!d || !S) return 0;
+  return carve_staging(d, B, T, S, nullptr).total;
+}
+
+extern "C" size_t tnt_decoder_loss_workspace_bytes(const tnt_decoder* d, int n_rows) {
+  return d ? adasoftmax_workspace_bytes(d->ada, n_rows, true) : 0;
+}
+
+extern "C" int tnt_decoder_score_host(tnt_decoder* D, const int64_t* ids_host, const int64_t* target_host,
+                                      const tnt_contexts* ch, float* out2_host, void* staging, size_t staging_bytes,
+                                      void* workspace, size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && ids_host && target_host && ch && out2_host && staging && workspace, "score_host: null pointer");
+  const int B = ch->B, T = ch->T;
+  Staging s = carve_staging(D, B, T, ch->S, staging);
+  if (s.total > staging_bytes) {
+    set_error("score_host: staging %zu < %zu", staging_bytes, s.total);
+    return TNT_ERR_WORKSPACE;
+  }
+  cudaStream_t st = as_stream(stream);
+  TNT_CUDA(cudaMemcpyAsync(s.ids, ids_host, sizeof(int64_t) * B * T, cudaMemcpyHostToDevice, st));
+  TNT_CUDA(cudaMemcpyAsync(s.tgt, target_host, sizeof(int64_t) * B * T, cudaMemcpyHostToDevice, st));
+  tnt_contexts cd = *ch;
+  for (int i = 0; i < D->cfg.n_sources; ++i) {
+    const size_t mb = static_cast<size_t>(ch->S[i]) * B * D->cfg.source_dim[i] * D->esz();
+    if (mb) TNT_CUDA(cudaMemcpyAsync(s.mem[i], ch->memory[i], mb, cudaMemcpyHostToDevice, st));
+    cd.memory[i] = s.mem[i];
+    if (ch->pad_mask[i] && ch->S[i]) {
+      TNT_CUDA(cudaMemcpyAsync(s.mask[i], ch->pad_mask[i], static_cast<size_t>(ch->S[i]) * B, cudaMemcpyHostToDevice, st));
+      cd.pad_mask[i] = s.mask[i];
+    } else {
+      cd.pad_mask[i] = nullptr;
+    }
+  }
+  const size_t fwd = carve_fwd(D, B, T, ch->S, nullptr, true).total;
+  const size_t loss = adasoftmax_workspace_bytes(D->ada, B * T, false);
+  if (fwd + loss > workspace_bytes) {
+    set_error("score_host: workspace %zu < %zu", workspace_bytes, fwd + loss);
+    return TNT_ERR_WORKSPACE;
+  }
+  TNT_TRY(tnt_decoder_forward(D, s.ids, &cd, s.X, nullptr, workspace, fwd, stream));
+  TNT_TRY(tnt_decoder_nll(D, s.X, s.tgt, B * T, s.out2, static_cast<char*>(workspace) + fwd, workspace_bytes - fwd, stream));
+  TNT_CUDA(cudaMemcpyAsync(out2_host, s.out2, 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
+  TNT_CUDA(cudaStreamSynchronize(st));
+  return TNT_OK;
+}

@@ -1,0 +1,407 @@
+// GEMM kernels behind tnt_linear_fwd / tnt_lse_fwd.
+//   bf16: persistent warp-specialised tcgen05 kernel -- TMA (128B swizzle) -> smem ring -> tcgen05.mma
+//         (single issuing thread, fp32 accumulators double-buffered in TMEM) -> tcgen05.ld epilogue.
+//   fp32: plain SIMT fp32 kernel (parity mode; also the in-library cross-check for the tcgen05 path).
+// Replaces GehringLinear / TiedLinear / F.linear: ttl/tell/modules/linear.py:7-50.
+#include <cuda.h>
+
+#include <algorithm>
+
+#include "gemm.cuh"
+#include "ptx.cuh"
+
+namespace tnt {
+
+// ============================================================================ tcgen05 kernel
+namespace tc {
+constexpr int BM = 128, BK = 64, UMMA_K = 16;
+constexpr int kThreads = 192;             // warp 0: TMA producer, warp 1: MMA issuer, warps 2-5: epilogue
+constexpr int A_STAGE_BYTES = BM * BK * 2;
+constexpr uint32_t kTmemCols = 512;       // 2 accumulator stages x 256 fp32 columns
+constexpr int kAccStride = 256;
+constexpr int kMaxStages = 8;
+constexpr int kSmemBudget = 220 * 1024;
+
+template <int EPI, typename TOut>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, GemmArgs g,
+               int BN, int stages, int n_tiles) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int stage_bytes = A_STAGE_BYTES + BN * BK * 2;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + stages * stage_bytes);
+  uint64_t* empty = full + kMaxStages;
+  uint64_t* tfull = empty + kMaxStages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int M = g.m_dyn ? min(g.M, __ldg(g.m_dyn)) : g.M;
+  const int m_tiles = (M + BM - 1) / BM;
+  const int total_tiles = g.groups * m_tiles * n_tiles;
+  const int num_kb = (g.K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmW);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < stages; ++s) {
+      ptx::mbar_init(&full[s], 1);
+      ptx::mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tfull[s], 1);
+      ptx::mbar_init(&tempty[s], 4);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc<kTmemCols>(tmem_slot);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int mt = tile % m_tiles, rest = tile / m_tiles, nt = rest % n_tiles, grp = rest / n_tiles;
+        const int ga = g.sa ? grp : 0, gw = g.sw ? grp : 0;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* sa = smem + s * stage_bytes;
+          ptx::mbar_arrive_expect_tx(&full[s], stage_bytes);
+          ptx::tma_load_3d(sa, &tmA, &full[s], kb * BK, mt * BM, ga);
+          ptx::tma_load_3d(sa + A_STAGE_BYTES, &tmW, &full[s], kb * BK, nt * BN, gw);
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      const uint32_t idesc = ptx::umma_idesc_bf16(BM, BN, 0, 0);
+      int s = 0, it = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const int as = it & 1;
+        const uint32_t aph = (it >> 1) & 1;
+        ptx::mbar_wait(&tempty[as], aph ^ 1);          // epilogue has drained this accumulator stage
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * kAccStride;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(&full[s], ph);                // TMA bytes have landed
+          ptx::tc_fence_after();
+          const uint32_t a_addr = ptx::smem_u32(smem + s * stage_bytes);
+          const uint32_t b_addr = a_addr + A_STAGE_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t ad = ptx::umma_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
+            const uint64_t bd = ptx::umma_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
+            ptx::umma_bf16_ss(d_tmem, ad, bd, idesc, (kb | k) != 0);
+          }
+          ptx::umma_commit(&empty[s]);                 // frees the smem slot when these MMAs retire
+          if (++s == stages) { s = 0; ph ^= 1; }
+        }
+        ptx::umma_commit(&tfull[as]);                  // accumulator complete -> epilogue
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------ epilogue warps (TMEM -> regs -> HBM)
+    const int q = warp & 3;                            // TMEM lane quadrant this warp may read
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      const int mt = tile % m_tiles, rest = tile / m_tiles, nt = rest % n_tiles, grp = rest / n_tiles;
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      ptx::mbar_wait(&tfull[as], aph);
+      ptx::tc_fence_after();
+      const int row = mt * BM + q * 32 + lane;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * kAccStride;
+      LseAcc la;
+      int tgt = -1;
+      if (EPI == EPI_LSE) {
+        la.init();
+        if (row < M && g.target) tgt = g.target[row];
+      }
+      for (int c = 0; c < BN / 32; ++c) {
+        const int n0 = nt * BN + c * 32;
+        if (n0 >= g.N) break;                          // warp-uniform
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(taddr + c * 32, v);
+        ptx::tmem_ld_wait();
+        if (row < M) {
+          float acc[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
+          if (EPI == EPI_LSE) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const int col = n0 + i;
+              if (col < g.N) {
+                const float z = acc[i] + (g.bias ? __ldg(g.bias + col) : 0.f);
+                if (col < g.n_lse) la.add(z, col, tgt);
+                else g.side[static_cast<long>(row) * g.side_ld + col - g.n_lse] = z;
+              }
+            }
+          } else {
+            epilogue_store<EPI, TOut, 32>(g, grp, row, n0, acc);
+          }
+        }
+      }
+      if (EPI == EPI_LSE && row < M)
+        g.partials[static_cast<long>(row) * g.n_tiles + nt] = make_float4(la.m, la.s, __int_as_float(la.arg), la.tz);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tempty[as]);
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) ptx::tmem_dealloc<kTmemCols>(tmem_base);
+}
+}  // namespace tc
+
+// ============================================================================ SIMT kernel
+namespace simt {
+constexpr int TM = 64, TN = 64, TK = 16;
+
+template <int EPI, typename TIn, typename TOut>
+__global__ void __launch_bounds__(256) gemm_simt_kernel(GemmArgs g) {
+  __shared__ float As[TK][TM + 4];
+  __shared__ float Ws[TK][TN + 4];
+  const int grp = blockIdx.z;
+  const int M = g.m_dyn ? min(g.M, __ldg(g.m_dyn)) : g.M;
+  const int m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
+  if (m0 >= M) return;
+  const TIn* A = reinterpret_cast<const TIn*>(g.a) + grp * g.sa;
+  const TIn* W = reinterpret_cast<const TIn*>(g.w) + grp * g.sw;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = 0; k0 < g.K; k0 += TK) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int idx = threadIdx.x + i * 256, r = idx >> 4, kk = idx & 15;
+      const bool kin = (k0 + kk) < g.K;
+      As[kk][r] = (kin && (m0 + r) < M) ? to_f(A[static_cast<long>(m0 + r) * g.lda + k0 + kk]) : 0.f;
+      Ws[kk][r] = (kin && (n0 + r) < g.N) ? to_f(W[static_cast<long>(n0 + r) * g.ldw + k0 + kk]) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < TK; ++kk) {
+      const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+      const float4 b = *reinterpret_cast<const float4*>(&Ws[kk][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int row = m0 + ty * 4 + i;
+    if (EPI == EPI_LSE) {
+      LseAcc la;
+      la.init();
+      const int tgt = (row < M && g.target) ? g.target[row] : -1;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int col = n0 + tx * 4 + j;
+        if (col < g.N) {
+          const float z = acc[i][j] + (g.bias ? __ldg(g.bias + col) : 0.f);
+          if (col < g.n_lse) la.add(z, col, tgt);
+          else if (row < M) g.side[static_cast<long>(row) * g.side_ld + col - g.n_lse] = z;
+        }
+      }
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) {
+        const float m2 = __shfl_xor_sync(0xffffffffu, la.m, o), s2 = __shfl_xor_sync(0xffffffffu, la.s, o);
+        const float t2 = __shfl_xor_sync(0xffffffffu, la.tz, o);
+        const int a2 = __shfl_xor_sync(0xffffffffu, la.arg, o);
+        la.merge(m2, s2, a2, t2);
+      }
+      if (tx == 0 && row < M)
+        g.partials[static_cast<long>(row) * g.n_tiles + blockIdx.x] =
+            make_float4(la.m, la.s, __int_as_float(la.arg), la.tz);
+    } else if (row < M) {
+      epilogue_store<EPI, TOut, 4>(g, grp, row, n0 + tx * 4, acc[i]);
+    }
+  }
+}
+}  // namespace simt
+
+// ============================================================================ host dispatch
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 3-D bf16 map {cols (K, contiguous), rows, groups}; box {64, box_rows, 1}; 128-byte swizzle.
+int make_tmap_bf16(CUtensorMap* tm, const void* base, long cols, long rows, long ld, long groups,
+                   long group_stride, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled entry point unavailable");
+    return TNT_ERR_CUDA;
+  }
+  if (groups < 1 || group_stride == 0) groups = 1;
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows),
+                        static_cast<cuuint64_t>(groups)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(ld) * 2,
+                           static_cast<cuuint64_t>(groups > 1 ? group_stride : ld * std::max<long>(rows, 1)) * 2};
+  cuuint32_t box[3] = {64, static_cast<cuuint32_t>(box_rows), 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d): base %p cols %ld rows %ld ld %ld groups %ld gstride %ld", (int)r,
+              base, cols, rows, ld, groups, group_stride);
+    return TNT_ERR_CUDA;
+  }
+  return TNT_OK;
+}
+
+static int pick_bn(int M, int N, int groups) {
+  const int m_tiles = (M + tc::BM - 1) / tc::BM;
+  const int sms = num_sms();
+  const int cands[4] = {256, 128, 64, 32};
+  for (int i = 0; i < 4; ++i) {
+    const int bn = cands[i];
+    if (i < 3 && N <= cands[i + 1]) continue;          // tile would be mostly padding
+    const long tiles = static_cast<long>(groups) * m_tiles * ((N + bn - 1) / bn);
+    if (tiles >= sms || i == 3) return bn;
+  }
+  return 32;
+}
+
+int gemm_tile_n(int dtype, int M, int N) { return dtype == TNT_BF16 ? pick_bn(M, N, 1) : simt::TN; }
+
+template <int EPI, typename TOut>
+static int launch_tc(const GemmArgs& g, int BN, cudaStream_t st) {
+  CUtensorMap tmA, tmW;
+  TNT_TRY(make_tmap_bf16(&tmA, g.a, g.K, g.M, g.lda, g.groups, g.sa, tc::BM));
+  TNT_TRY(make_tmap_bf16(&tmW, g.w, g.K, g.N, g.ldw, g.groups, g.sw, BN));
+  const int stage_bytes = tc::A_STAGE_BYTES + BN * tc::BK * 2;
+  const int stages = std::min(tc::kMaxStages, (tc::kSmemBudget - 2048) / stage_bytes);
+  const int smem = stages * stage_bytes + 1024 + 512;
+  const int n_tiles = (g.N + BN - 1) / BN;
+  const long tiles = static_cast<long>(g.groups) * ((g.M + tc::BM - 1) / tc::BM) * n_tiles;
+  const int grid = static_cast<int>(std::min<long>(tiles, num_sms()));
+  auto kern = tc::gemm_tc_kernel<EPI, TOut>;
+  static bool attr_set = false;   // per instantiation
+  if (!attr_set) {
+    TNT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBudget + 4096));
+    attr_set = true;
+  }
+  kern<<<grid, tc::kThreads, smem, st>>>(tmA, tmW, g, BN, stages, n_tiles);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+template <int EPI, typename TIn, typename TOut>
+static int launch_simt(const GemmArgs& g, cudaStream_t st) {
+  dim3 grid((g.N + simt::TN - 1) / simt::TN, (g.M + simt::TM - 1) / simt::TM, g.groups);
+  simt::gemm_simt_kernel<EPI, TIn, TOut><<<grid, 256, 0, st>>>(g);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+template <int EPI>
+static int dispatch_dtype(const GemmArgs& g, int dt_in, int dt_out, int BN, bool force_simt, cudaStream_t st) {
+  if (dt_in == TNT_BF16 && !force_simt) {
+    if (dt_out == TNT_BF16) return launch_tc<EPI, bf16>(g, BN, st);
+    return launch_tc<EPI, float>(g, BN, st);
+  }
+  if (dt_in == TNT_BF16) {
+    if (dt_out == TNT_BF16) return launch_simt<EPI, bf16, bf16>(g, st);
+    return launch_simt<EPI, bf16, float>(g, st);
+  }
+  if (dt_out == TNT_F32) return launch_simt<EPI, float, float>(g, st);
+  return launch_simt<EPI, float, bf16>(g, st);
+}
+
+static bool g_force_simt = false;   // test hook: run bf16 problems on the SIMT kernel (cross-check)
+void gemm_force_simt(bool on) { g_force_simt = on; }
+
+int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* lse, int* n_tiles_out,
+                cudaStream_t st) {
+  TNT_CHECK_ARG(p && p->a && p->w, "linear: null operand");
+  TNT_CHECK_ARG(p->M >= 0 && p->N > 0 && p->K > 0, "linear: bad shape M=%d N=%d K=%d", p->M, p->N, p->K);
+  const int epi = epi_override >= 0 ? epi_override : p->epilogue;
+  TNT_CHECK_ARG(epi == EPI_LSE || p->c, "linear: null output");
+  TNT_CHECK_ARG(p->dtype_in == TNT_F32 || p->dtype_in == TNT_BF16, "linear: dtype_in");
+  TNT_CHECK_ARG(epi != EPI_GLU || (p->N % 2 == 0), "linear: GLU needs an even N");
+  TNT_CHECK_ARG(epi != EPI_RESIDUAL || p->residual, "linear: residual epilogue without residual");
+  if (p->M == 0) return TNT_OK;
+  GemmArgs g;
+  g.a = p->a; g.w = p->w; g.bias = p->bias; g.res = p->residual; g.c = p->c;
+  g.lda = p->lda; g.ldw = p->ldw; g.ldr = p->ldr; g.ldc = p->ldc;
+  g.M = p->M; g.N = p->N; g.K = p->K;
+  g.m_dyn = p->m_dyn;
+  g.groups = p->groups > 0 ? p->groups : 1;
+  g.sa = p->stride_a; g.sw = p->stride_w; g.sbias = p->stride_bias; g.sres = p->stride_res; g.sc = p->stride_c;
+  g.target = lse ? lse->target : nullptr;
+  g.partials = lse ? lse->partials : nullptr;
+  g.n_lse = lse ? lse->n_lse : 0;
+  g.side = lse ? lse->side : nullptr;
+  g.side_ld = lse ? lse->side_ld : 0;
+  g.n_tiles = 0;
+  TNT_CHECK_ARG(epi != EPI_LSE || (lse && lse->partials && (lse->n_lse >= p->N || lse->side)), "lse: missing buffers");
+  const size_t eo = dtype_size(p->dtype_out);
+  const long vec = 16 / static_cast<long>(eo);
+  g.vec_ok = epi == EPI_LSE ? 0
+                            : (aligned16(p->c) && p->ldc % vec == 0 && g.sc % vec == 0 &&
+                               (epi != EPI_RESIDUAL ||
+                                (aligned16(p->residual) && p->ldr % vec == 0 && g.sres % vec == 0)));
+  const bool use_tc = p->dtype_in == TNT_BF16 && !g_force_simt;
+  int BN = simt::TN;
+  if (use_tc) {
+    TNT_CHECK_ALIGN(aligned16(p->a) && aligned16(p->w) && p->lda % 8 == 0 && p->ldw % 8 == 0 && g.sa % 8 == 0 &&
+                        g.sw % 8 == 0,
+                    "linear(bf16): A / W must be 16-byte aligned with leading dimensions multiple of 8 (lda=%ld ldw=%ld)",
+                    (long)p->lda, (long)p->ldw);
+    BN = pick_bn(g.M, g.N, g.groups);
+  }
+  g.n_tiles = (g.N + BN - 1) / BN;
+  if (n_tiles_out) *n_tiles_out = g.n_tiles;
+  switch (epi) {
+    case EPI_NONE: return dispatch_dtype<EPI_NONE>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
+    case EPI_RELU: return dispatch_dtype<EPI_RELU>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
+    case EPI_GLU: return dispatch_dtype<EPI_GLU>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
+    case EPI_RESIDUAL: return dispatch_dtype<EPI_RESIDUAL>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
+    case EPI_LSE: return dispatch_dtype<EPI_LSE>(g, p->dtype_in, TNT_F32, BN, g_force_simt, st);
+  }
+  set_error("linear: unknown epilogue %d", epi);
+  return TNT_ERR_ARG;
+}
+
+}  // namespace tnt
+
+extern "C" int tnt_linear_fwd(const tnt_linear_params* p, tnt_stream stream) {
+  return tnt::launch_gemm(p, -1, nullptr, nullptr, tnt::as_stream(stream));
+}
+extern "C" void tnt_debug_force_simt_gemm(int on) { tnt::gemm_force_simt(on != 0); }

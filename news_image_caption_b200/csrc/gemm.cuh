@@ -1,0 +1,130 @@
+// Device-side argument block + epilogues shared by the tcgen05 GEMM (bf16) and the SIMT GEMM (fp32).
+#pragma once
+#include "common.cuh"
+
+namespace tnt {
+
+enum : int { EPI_NONE = 0, EPI_RELU = 1, EPI_GLU = 2, EPI_RESIDUAL = 3, EPI_LSE = 4 };
+
+struct GemmArgs {
+  const void* a; const void* w; const float* bias; const void* res; void* c;
+  long lda, ldw, ldr, ldc;
+  int M, N, K;
+  const int* m_dyn;
+  int groups;
+  long sa, sw, sbias, sres, sc;
+  int vec_ok;               // C (and residual) rows allow 16-byte vector access
+  // EPI_LSE only
+  const int* target;        // [M] cluster-local target column or < 0
+  float4* partials;         // [M, n_tiles] (max, sumexp, argmax bits, target logit or 0)
+  int n_tiles;
+  int n_lse;                // columns [0, n_lse) take part in max / sum / argmax ...
+  float* side; long side_ld;  // ... columns [n_lse, N) are written raw to side[row, col - n_lse]
+};
+
+struct LseExtra {
+  const int* target; float4* partials; int n_lse; float* side; long side_ld;
+};
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+
+// One thread owns NC consecutive accumulator columns [n0, n0+NC) of row m (n0 % NC == 0).
+template <int EPI, typename TOut, int NC>
+__device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m, int n0, float (&acc)[NC]) {
+  static_assert(NC % 8 == 0 || NC == 4, "NC");
+  const float* bias = g.bias ? g.bias + grp * g.sbias : nullptr;
+  if (bias) {
+#pragma unroll
+    for (int i = 0; i < NC; ++i)
+      if (n0 + i < g.N) acc[i] += __ldg(bias + n0 + i);
+  }
+  TOut* crow = reinterpret_cast<TOut*>(g.c) + grp * g.sc + static_cast<long>(m) * g.ldc;
+  if (EPI == EPI_GLU) {
+    constexpr int NO = NC / 2;
+    float o[NO];
+#pragma unroll
+    for (int i = 0; i < NO; ++i) o[i] = acc[2 * i] * sigmoidf_(acc[2 * i + 1]);
+    const int c0 = n0 >> 1, NOUT = g.N >> 1;
+    if (NO % 8 == 0 && g.vec_ok && c0 + NO <= NOUT) {
+#pragma unroll
+      for (int i = 0; i < NO; i += 8) {
+        float t[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[j] = o[i + j];
+        store8(crow + c0 + i, t);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < NO; ++i)
+        if (c0 + i < NOUT) crow[c0 + i] = from_f<TOut>(o[i]);
+    }
+    return;
+  }
+  if (EPI == EPI_RESIDUAL) {
+    const TOut* rrow = reinterpret_cast<const TOut*>(g.res) + grp * g.sres + static_cast<long>(m) * g.ldr;
+    if (NC % 8 == 0 && g.vec_ok && n0 + NC <= g.N) {
+#pragma unroll
+      for (int i = 0; i < NC; i += 8) {
+        float t[8];
+        load8(rrow + n0 + i, t);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i + j] += t[j];
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < NC; ++i)
+        if (n0 + i < g.N) acc[i] += to_f(rrow[n0 + i]);
+    }
+  }
+  if (EPI == EPI_RELU) {
+#pragma unroll
+    for (int i = 0; i < NC; ++i) acc[i] = fmaxf(acc[i], 0.f);
+  }
+  if (NC % 8 == 0 && g.vec_ok && n0 + NC <= g.N) {
+#pragma unroll
+    for (int i = 0; i < NC; i += 8) {
+      float t[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t[j] = acc[i + j];
+      store8(crow + n0 + i, t);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < NC; ++i)
+      if (n0 + i < g.N) crow[n0 + i] = from_f<TOut>(acc[i]);
+  }
+}
+
+// running (max, sumexp, argmax, target-logit) over a run of columns of one row
+struct LseAcc {
+  float m, s, tz;
+  int arg;
+  __device__ __forceinline__ void init() { m = -INFINITY; s = 0.f; tz = 0.f; arg = -1; }
+  __device__ __forceinline__ void add(float z, int col, int tgt) {
+    if (z > m) {
+      s = s * __expf(m - z) + 1.f;      // m = -inf -> exp(-inf) = 0
+      m = z;
+      arg = col;
+    } else {
+      s += __expf(z - m);
+    }
+    if (col == tgt) tz = z;
+  }
+  __device__ __forceinline__ void merge(float m2, float s2, int arg2, float tz2) {
+    if (m2 > m || (m2 == m && arg2 >= 0 && (arg < 0 || arg2 < arg))) {
+      s = s * ((m == -INFINITY) ? 0.f : __expf(m - m2)) + s2;
+      m = m2;
+      arg = arg2;
+    } else if (m2 != -INFINITY) {
+      s += s2 * __expf(m2 - m);
+    }
+    tz += tz2;
+  }
+};
+
+// host dispatch (gemm.cu)
+int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* lse, int* n_tiles_out,
+                cudaStream_t st);
+int gemm_tile_n(int dtype, int M, int N);     // N-tile width the dispatcher will use (for partial sizing)
+
+}  // namespace tnt

@@ -1,0 +1,373 @@
+"""Host-side mirror of the reference decoder interface, backed by the C-ABI engine.
+
+`DynamicConvDecoder` keeps the reference's constructor meaning, `forward(prev_target, contexts,
+incremental_state)` signature, `get_normalized_probs`, and -- through an attribute tree with the same
+names -- the reference's `state_dict` keys, so a reference checkpoint loads unchanged
+(ttl/tell/models/decoder_flattened.py:22-207, decoder_faces_objects.py:21-208).  `AdaptiveLoss` mirrors
+ttl/tell/modules/criteria/adaptive_loss.py:10-91.  torch is used for device memory and the stream only.
+"""
+import ctypes as C
+import math
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from ._lib import TNT_BF16, TNT_F32
+
+SOURCE_ORDER = ('image', 'article', 'faces', 'obj')          # concat order, decoder_faces_objects.py:296-383
+DEFAULT_SOURCE_DIM = {'image': 2048, 'article': 1024, 'faces': 512, 'obj': 2048}
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _dtype_code(dtype):
+    if dtype in (torch.bfloat16, 'bf16', TNT_BF16):
+        return TNT_BF16, torch.bfloat16
+    if dtype in (torch.float32, 'fp32', 'f32', TNT_F32):
+        return TNT_F32, torch.float32
+    raise ValueError('dtype must be torch.bfloat16 or torch.float32')
+
+
+def _register(root, key, tensor):
+    """Registers `tensor` as parameter `key` (dotted) under nested container modules."""
+    mod = root
+    parts = key.split('.')
+    for p in parts[:-1]:
+        if not hasattr(mod, p):
+            mod.add_module(p, nn.Module())
+        mod = getattr(mod, p)
+    mod.register_parameter(parts[-1], nn.Parameter(tensor, requires_grad=False))
+
+
+def reference_shapes(d, heads, ffn, kernels, vocab, cutoffs, sources, source_dim, n_pos=513):
+    """state_dict layout of the reference decoder."""
+    sh = {}
+    lo = 0
+    for i, hi in enumerate(cutoffs):
+        sh['embedder.token_embedder_adaptive.embeddings.%d.0.weight' % i] = (hi - lo, d)
+        sh['embedder.token_embedder_adaptive.embeddings.%d.1.weight' % i] = (d, d)
+        lo = hi
+    sh['embedder.token_embedder_position.weights'] = (n_pos, d)
+    for l, K in enumerate(kernels):
+        p = 'layers.%d.' % l
+        for name, (o, i) in (('linear1', (2 * d, d)), ('linear2', (d, d)), ('context_fc', (d, len(sources) * d)),
+                             ('fc1', (ffn, d)), ('fc2', (d, ffn))):
+            sh[p + name + '.bias'] = (o,)
+            sh[p + name + '.weight_g'] = (o, 1)
+            sh[p + name + '.weight_v'] = (o, i)
+        sh[p + 'conv.weight_linear.weight'] = (heads * K, d)
+        for ln in ('conv_layer_norm', 'final_layer_norm'):
+            sh[p + ln + '.weight'] = (d,)
+            sh[p + ln + '.bias'] = (d,)
+        for s in sources:
+            a = p + 'context_attns.%s.' % s
+            kd = source_dim[s]
+            if kd == d:
+                sh[a + 'in_proj_weight'] = (3 * d, d)
+            else:
+                sh[a + 'k_proj_weight'] = (d, kd)
+                sh[a + 'v_proj_weight'] = (d, kd)
+                sh[a + 'q_proj_weight'] = (d, d)
+            sh[a + 'in_proj_bias'] = (3 * d,)
+            sh[a + 'bias_k'] = (1, 1, d)
+            sh[a + 'bias_v'] = (1, 1, d)
+            sh[a + 'out_proj.weight'] = (d, d)
+            sh[a + 'out_proj.bias'] = (d,)
+            sh[p + 'context_attn_lns.%s.weight' % s] = (d,)
+            sh[p + 'context_attn_lns.%s.bias' % s] = (d,)
+    sh['adaptive_softmax.head.word_proj.weight'] = (cutoffs[0], d)
+    if len(cutoffs) > 1:
+        sh['adaptive_softmax.head.class_proj.weight'] = (len(cutoffs) - 1, d)
+    for i in range(len(cutoffs) - 1):
+        sh['adaptive_softmax.tail.%d.0.weight' % i] = (d, d)
+        sh['adaptive_softmax.tail.%d.2.weight' % i] = (cutoffs[i + 1] - cutoffs[i], d)
+    return sh
+
+
+IGNORED_KEYS = ('version', 'adaptive_softmax.version', 'adaptive_softmax.head._float_tensor')
+
+
+class DynamicConvDecoder(nn.Module):
+    """B200 engine behind the reference `DynamicConvDecoder` / `DynamicConvFacesObjectsDecoder` API
+    (post-LN, GLU, dynamic conv, weight_softmax, adaptive softmax with tied weights: the configuration
+    every shipped experiment uses, ttl/expt/*/config.yaml)."""
+
+    def __init__(self, decoder_output_dim=1024, decoder_attention_heads=16, decoder_ffn_embed_dim=4096,
+                 decoder_kernel_size_list=(3, 7, 15, 31), vocab_size=50265, adaptive_softmax_cutoff=(5000, 20000),
+                 sources=('image', 'article'), source_dim=None, padding_idx=1, max_positions=513,
+                 dtype=torch.bfloat16, device='cuda', init_std=None):
+        super().__init__()
+        self.d, self.heads, self.ffn = decoder_output_dim, decoder_attention_heads, decoder_ffn_embed_dim
+        self.kernels = list(decoder_kernel_size_list)
+        self.cutoffs = list(adaptive_softmax_cutoff) + [vocab_size]
+        self.vocab = vocab_size
+        self.sources = [s for s in SOURCE_ORDER if s in sources]
+        self.source_dim = dict(DEFAULT_SOURCE_DIM)
+        self.source_dim.update(source_dim or {})
+        self.pad = padding_idx
+        self.max_positions = max_positions
+        self.dtype_code, self.torch_dtype = _dtype_code(dtype)
+        shapes = reference_shapes(self.d, self.heads, self.ffn, self.kernels, self.vocab, self.cutoffs,
+                                  self.sources, self.source_dim, max_positions)
+        for k, shp in shapes.items():
+            _register(self, k, torch.zeros(shp, dtype=torch.float32, device=device))
+        self._handle = None
+        self._weights = None
+        self._dirty = True
+        self._ws = {}
+        self.register_load_state_dict_post_hook(lambda m, ik: setattr(m, '_dirty', True))
+
+    # ------------------------------------------------------------------ state_dict compatibility
+    def load_reference_state_dict(self, sd):
+        """Loads a reference checkpoint: tied output weights appear under both names there; buffers
+        that carry no numbers (`version`, `_float_tensor`) are ignored."""
+        own = dict(self.named_parameters())
+        missing = [k for k in own if k not in sd]
+        if missing:
+            raise KeyError('reference state_dict lacks %s' % missing[:4])
+        unexpected = [k for k in sd if k not in own and k not in IGNORED_KEYS]
+        if unexpected:
+            raise KeyError('unexpected keys %s' % unexpected[:4])
+        with torch.no_grad():
+            for k, p in own.items():
+                p.copy_(sd[k].to(p.device, torch.float32).reshape(p.shape))
+        self._dirty = True
+        return self
+
+    # ------------------------------------------------------------------ engine plumbing
+    def _config(self):
+        c = _lib.DecoderConfig()
+        c.n_layers, c.d, c.heads, c.ffn, c.vocab = len(self.kernels), self.d, self.heads, self.ffn, self.vocab
+        for i, k in enumerate(self.kernels):
+            c.kernels[i] = k
+        c.n_sources = len(self.sources)
+        for i, s in enumerate(self.sources):
+            c.source_names[i].value = s.encode()
+            c.source_dim[i] = self.source_dim[s]
+        c.n_clusters = len(self.cutoffs)
+        for i, v in enumerate(self.cutoffs):
+            c.cutoffs[i] = v
+        c.pad_idx, c.max_positions, c.dtype = self.pad, self.max_positions, self.dtype_code
+        return c
+
+    def prepare(self):
+        """(Re)builds the prepared weights from the current parameters (weight-norm fold, fusion)."""
+        L = _lib.lib()
+        _lib.require_device()
+        if self._handle is None:
+            cfg = self._config()
+            self._handle = L.tnt_decoder_create(C.byref(cfg))
+            if not self._handle:
+                _lib.check(-1, 'tnt_decoder_create')
+            nbytes = L.tnt_decoder_weight_bytes(self._handle)
+            self._weights = torch.empty(nbytes, dtype=torch.uint8, device='cuda')
+            _lib.check(L.tnt_decoder_bind_weights(self._handle, _ptr(self._weights), nbytes), 'bind_weights')
+        keep = []
+        for k, p in self.named_parameters():
+            t = p.detach().contiguous()
+            keep.append(t)
+            shp = (C.c_int64 * t.dim())(*t.shape)
+            _lib.check(L.tnt_decoder_load(self._handle, k.encode(), _ptr(t), shp, t.dim(), _stream()), 'load ' + k)
+        _lib.check(L.tnt_decoder_finalize(self._handle, _stream()), 'tnt_decoder_finalize')
+        torch.cuda.current_stream().synchronize()     # `keep` may be released after this
+        self._dirty = False
+
+    def _h(self):
+        if self._dirty or self._handle is None:
+            self.prepare()
+        return self._handle
+
+    def __del__(self):
+        try:
+            if self._handle:
+                _lib.lib().tnt_decoder_destroy(self._handle)
+        except Exception:
+            pass
+
+    def _workspace(self, key, nbytes):
+        t = self._ws.get(key)
+        if t is None or t.numel() < nbytes:
+            t = torch.empty(nbytes + 256, dtype=torch.uint8, device='cuda')
+            self._ws[key] = t
+        return t
+
+    def _contexts(self, contexts, B, T):
+        c = _lib.Contexts()
+        c.B, c.T = B, T
+        keep = []
+        for i, s in enumerate(self.sources):
+            mem = contexts[s]
+            if mem.dim() != 3 or mem.shape[1] != B or mem.shape[2] != self.source_dim[s]:
+                raise ValueError('context %s must be [S, %d, %d], got %s' % (s, B, self.source_dim[s],
+                                                                             tuple(mem.shape)))
+            mem = mem.to(self.torch_dtype).contiguous()
+            mask = contexts.get(s + '_mask')
+            c.S[i] = mem.shape[0]
+            c.memory[i] = mem.data_ptr() if mem.numel() else None
+            if mask is not None and mem.shape[0] > 0:
+                mask = mask.to(torch.bool).contiguous()
+                if tuple(mask.shape) != (B, mem.shape[0]):
+                    raise ValueError('%s_mask must be [B, S]' % s)
+                c.pad_mask[i] = mask.data_ptr()
+            keep += [mem, mask]
+        return c, keep
+
+    # ------------------------------------------------------------------ reference API
+    def forward(self, prev_target, contexts, incremental_state=None, need_attn=True):
+        """ids [B,T] (or {'roberta': ids}) -> (X [B,T,d], {'attn': [B,T,S_article+2] | None}) --
+        decoder_flattened.py:96-146.  `incremental_state` selects single-step decoding and is handled
+        by `generate()`; passing one here raises (the engine owns the incremental buffers)."""
+        if incremental_state is not None:
+            raise NotImplementedError('step-wise decoding is driven by DynamicConvDecoder.generate()')
+        ids = prev_target['roberta'] if isinstance(prev_target, dict) else prev_target
+        ids = ids.to('cuda', torch.long).contiguous()
+        B, T = ids.shape
+        L, h = _lib.lib(), self._h()
+        ctx, keep = self._contexts(contexts, B, T)
+        S = (C.c_int * 4)(*[ctx.S[i] for i in range(4)])
+        ws = self._workspace('fwd', L.tnt_decoder_workspace_bytes(h, B, T, S))
+        X = torch.empty(B, T, self.d, dtype=self.torch_dtype, device='cuda')
+        attn = None
+        if need_attn and 'article' in self.sources:
+            attn = torch.empty(B, T, ctx.S[self.sources.index('article')] + 2, dtype=torch.float32, device='cuda')
+        _lib.check(L.tnt_decoder_forward(h, _ptr(ids), C.byref(ctx), _ptr(X), _ptr(attn), _ptr(ws), ws.numel(),
+                                         _stream()), 'tnt_decoder_forward')
+        return X, {'attn': attn, 'inner_states': None}
+
+    def nll(self, X, target):
+        """AdaptiveSoftmax.forward + AdaptiveLoss(reduction='sum'): (loss_sum [1], n_non_pad) as device tensors."""
+        L, h = _lib.lib(), self._h()
+        X = X.to(self.torch_dtype).contiguous().view(-1, self.d)
+        target = target.to('cuda', torch.long).contiguous().view(-1)
+        n = X.shape[0]
+        ws = self._workspace('loss', L.tnt_decoder_loss_workspace_bytes(h, n))
+        out = torch.empty(2, dtype=torch.float32, device='cuda')
+        _lib.check(L.tnt_decoder_nll(h, _ptr(X), _ptr(target), n, _ptr(out), _ptr(ws), ws.numel(), _stream()),
+                   'tnt_decoder_nll')
+        return out
+
+    def get_normalized_probs(self, net_output, log_probs=True, sample=None):
+        """decoder_flattened.py:187-200 -> AdaptiveSoftmax.get_log_prob (softmax.py:193-222)."""
+        X = net_output[0]
+        B, T, _ = X.shape
+        L, h = _lib.lib(), self._h()
+        Xc = X.to(self.torch_dtype).contiguous().view(-1, self.d)
+        ws = self._workspace('loss', L.tnt_decoder_loss_workspace_bytes(h, B * T))
+        out = torch.empty(B, T, self.vocab, dtype=torch.float32, device='cuda')
+        _lib.check(L.tnt_decoder_log_prob(h, _ptr(Xc), B * T, _ptr(out), _ptr(ws), ws.numel(), _stream()),
+                   'tnt_decoder_log_prob')
+        return out if log_probs else out.exp_()
+
+    def generate(self, seed, contexts, gen_len=100, eos=2, trim=True):
+        """Greedy `_generate` (transformer_flattened.py:238-325): returns (log_probs [B,L'], ids [B,L'+1]);
+        with trim=True the outputs stop at the step after which every row had produced EOS, as the
+        reference's early `break` does."""
+        seed = seed.to('cuda', torch.long)
+        if seed.dim() == 2:
+            seed = seed[:, -1]
+        seed = seed.contiguous()
+        B = seed.shape[0]
+        L, h = _lib.lib(), self._h()
+        ctx, keep = self._contexts(contexts, B, 1)
+        S = (C.c_int * 4)(*[ctx.S[i] for i in range(4)])
+        ws = self._workspace('gen', L.tnt_decoder_generate_workspace_bytes(h, B, gen_len, S))
+        ids = torch.empty(B, gen_len + 1, dtype=torch.long, device='cuda')
+        lp = torch.empty(B, gen_len, dtype=torch.float32, device='cuda')
+        steps = C.c_int(0)
+        _lib.check(L.tnt_decoder_generate(h, _ptr(seed), C.byref(ctx), gen_len, eos, _ptr(ids), _ptr(lp),
+                                          C.byref(steps) if trim else None, _ptr(ws), ws.numel(), _stream()),
+                   'tnt_decoder_generate')
+        if trim:
+            n = steps.value
+            return lp[:, :n], ids[:, :n + 1]
+        return lp, ids
+
+    def score_host(self, ids_host, target_host, contexts_host):
+        """End-to-end teacher-forced scoring from PINNED HOST buffers (ids/targets int64 [B,T], contexts in
+        the engine dtype, masks bool): H2D copies + forward + AdaptiveLoss + D2H of (loss_sum, n_tokens),
+        synchronous.  Returns (loss_sum, n_tokens) as Python floats."""
+        L, h = _lib.lib(), self._h()
+        B, T = ids_host.shape
+        c = _lib.Contexts()
+        c.B, c.T = B, T
+        for i, s in enumerate(self.sources):
+            mem = contexts_host[s]
+            if mem.dtype != self.torch_dtype or not mem.is_contiguous() or mem.is_cuda:
+                raise ValueError('host context %s must be a contiguous CPU tensor of dtype %s' % (s, self.torch_dtype))
+            c.S[i] = mem.shape[0]
+            c.memory[i] = mem.data_ptr()
+            m = contexts_host.get(s + '_mask')
+            c.pad_mask[i] = m.data_ptr() if m is not None else None
+        S = (C.c_int * 4)(*[c.S[i] for i in range(4)])
+        stg = self._workspace('stage', L.tnt_decoder_score_host_staging_bytes(h, B, T, S))
+        ws = self._workspace('score', L.tnt_decoder_workspace_bytes(h, B, T, S) +
+                             L.tnt_decoder_loss_workspace_bytes(h, B * T))
+        if getattr(self, '_out2', None) is None:
+            self._out2 = torch.zeros(2, dtype=torch.float32).pin_memory()
+        _lib.check(L.tnt_decoder_score_host(h, _ptr(ids_host), _ptr(target_host), C.byref(c), _ptr(self._out2),
+                                            _ptr(stg), stg.numel(), _ptr(ws), ws.numel(), _stream()),
+                   'tnt_decoder_score_host')
+        return float(self._out2[0]), float(self._out2[1])
+
+
+class AdaptiveLoss(nn.Module):
+    """criteria/adaptive_loss.py:10-91: forward(adaptive_softmax_owner, net_output, target, reduction='sum')
+    -> (loss [1], sample_size).  `adaptive_softmax_owner` is the engine decoder (it owns the tied head)."""
+
+    def __init__(self, padding_idx=1):
+        super().__init__()
+        self.padding_idx = padding_idx
+
+    def forward(self, decoder, net_output, decoder_target, reduction='sum'):
+        if reduction != 'sum':
+            raise NotImplementedError('reduction=%r' % reduction)
+        out = decoder.nll(net_output[0], decoder_target)
+        return out[:1], int(out[1].item())
+
+
+def sinusoid_table(n, d, padding_idx=1):
+    """tensor2tensor sinusoids [sin | cos] with the padding row zeroed --
+    ttl/tell/modules/token_embedders/positional.py:125-165 (the reference builds this buffer at init)."""
+    half = d // 2
+    inc = math.log(10000.0) / (half - 1)
+    inv = torch.exp(torch.arange(half, dtype=torch.float) * -inc)
+    ang = torch.arange(n, dtype=torch.float)[:, None] * inv[None, :]
+    tab = torch.cat([ang.sin(), ang.cos()], 1)
+    if d % 2 == 1:
+        tab = torch.cat([tab, torch.zeros(n, 1)], 1)
+    tab[padding_idx] = 0
+    return tab
+
+
+def random_state_dict(d=1024, heads=16, ffn=4096, kernels=(3, 7, 15, 31), vocab=50265, cutoffs=(5000, 20000, 50265),
+                      sources=('image', 'article'), source_dim=None, seed=0, n_pos=513):
+    """Random-init weights with the reference's state_dict layout (synthetic benchmark / test weights;
+    no checkpoint exists offline).  Scales keep activations O(1); tied output rows alias the embedding
+    bands as in the reference (softmax.py:83-86,111-132)."""
+    sdim = dict(DEFAULT_SOURCE_DIM)
+    sdim.update(source_dim or {})
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+    for k, shp in reference_shapes(d, heads, ffn, list(kernels), vocab, list(cutoffs), list(sources), sdim,
+                                   n_pos).items():
+        if k.endswith('weight_g'):
+            sd[k] = torch.rand(shp, generator=g) + 0.5
+        elif (k.endswith('layer_norm.weight') or ('_lns.' in k and k.endswith('weight'))):
+            sd[k] = 1 + 0.1 * torch.randn(shp, generator=g)
+        elif len(shp) == 1 or 'bias' in k:
+            sd[k] = 0.1 * torch.randn(shp, generator=g)
+        elif 'token_embedder_position' in k:
+            sd[k] = sinusoid_table(shp[0], shp[1])
+        else:
+            sd[k] = torch.randn(shp, generator=g) * (shp[-1] ** -0.5)
+    sd['adaptive_softmax.head.word_proj.weight'] = sd['embedder.token_embedder_adaptive.embeddings.0.0.weight']
+    for i in range(len(cutoffs) - 1):
+        sd['adaptive_softmax.tail.%d.2.weight' % i] = sd['embedder.token_embedder_adaptive.embeddings.%d.0.weight' % (i + 1)]
+    return sd

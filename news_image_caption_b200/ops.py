@@ -1,0 +1,192 @@
+"""Thin Python callers of the fine-grained C-ABI ops (include/tnt_b200.h).  torch tensors only supply the
+device memory and the stream; every computation happens in libtnt_b200.so."""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import (EPI_GLU, EPI_NONE, EPI_RELU, EPI_RESIDUAL, MASK_KEY_PADDING, MASK_NONE, MASK_V2, TNT_BF16,
+                   TNT_F32)
+
+
+def _code(t):
+    if t.dtype == torch.bfloat16:
+        return TNT_BF16
+    if t.dtype == torch.float32:
+        return TNT_F32
+    raise TypeError('tensor dtype must be float32 or bfloat16, got %s' % t.dtype)
+
+
+def _p(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _st():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _cuda(t):
+    if not t.is_cuda:
+        raise TypeError('tnt ops need CUDA tensors (there is no CPU path)')
+    return t
+
+
+def linear(a, w, bias=None, epilogue=EPI_NONE, residual=None, out_dtype=None):
+    """epilogue(a[M,K] @ w[N,K]^T + bias).  For EPI_GLU `w`/`bias` rows must be pair-interleaved."""
+    a, w = _cuda(a).contiguous(), _cuda(w).contiguous()
+    M, K = a.shape
+    N = w.shape[0]
+    out_dtype = out_dtype or a.dtype
+    n_out = N // 2 if epilogue == EPI_GLU else N
+    c = torch.empty(M, n_out, dtype=out_dtype, device=a.device)
+    p = _lib.LinearParams()
+    p.a, p.lda, p.w, p.ldw = a.data_ptr(), K, w.data_ptr(), K
+    p.bias = bias.data_ptr() if bias is not None else None
+    if residual is not None:
+        residual = residual.contiguous()
+        p.residual, p.ldr = residual.data_ptr(), residual.shape[1]
+    p.c, p.ldc, p.M, p.N, p.K, p.groups = c.data_ptr(), n_out, M, N, K, 1
+    p.dtype_in, p.dtype_out, p.epilogue = _code(a), _code(c), epilogue
+    _lib.check(_lib.lib().tnt_linear_fwd(C.byref(p), _st()), 'tnt_linear_fwd')
+    return c
+
+
+def wn_fold(v, g=None, glu_interleave=False, dtype=torch.float32):
+    v = _cuda(v).float().contiguous()
+    out = torch.empty(v.shape, dtype=dtype, device=v.device)
+    gg = g.float().contiguous() if g is not None else None
+    _lib.check(_lib.lib().tnt_wn_fold(_p(v), _p(gg), _p(out), v.shape[0], v.shape[1], int(glu_interleave),
+                                      _code(out), _st()), 'tnt_wn_fold')
+    return out
+
+
+def glu_interleave_bias(b):
+    b = _cuda(b).float().contiguous()
+    out = torch.empty_like(b)
+    _lib.check(_lib.lib().tnt_glu_interleave_bias(_p(b), _p(out), b.numel(), _st()), 'tnt_glu_interleave_bias')
+    return out
+
+
+def dynconv(x, logits, H, K, hist=None):
+    """x [T,B,C], logits [T,B,H*K] -> y [T,B,C]; hist [h,B,C] = previous conv inputs (oldest first)."""
+    x, logits = _cuda(x).contiguous(), logits.contiguous()
+    T, B, Cc = x.shape
+    y = torch.empty_like(x)
+    p = _lib.DynconvParams()
+    p.x, p.ldx, p.logits, p.ldl, p.y, p.ldy = x.data_ptr(), Cc, logits.data_ptr(), logits.shape[-1], y.data_ptr(), Cc
+    if hist is not None and hist.shape[0] > 0:
+        hist = hist.contiguous()
+        p.hist, p.hist_len = hist.data_ptr(), hist.shape[0]
+    p.T, p.B, p.C, p.H, p.K, p.dtype = T, B, Cc, H, K, _code(x)
+    _lib.check(_lib.lib().tnt_dynconv_fwd(C.byref(p), _st()), 'tnt_dynconv_fwd')
+    return y
+
+
+def dynconv_bwd(x, logits, dy, H, K):
+    x, logits, dy = _cuda(x).contiguous(), logits.contiguous(), dy.contiguous()
+    T, B, Cc = x.shape
+    dx, dl = torch.empty_like(x), torch.empty_like(logits)
+    p = _lib.DynconvBwdParams()
+    p.x, p.ldx, p.logits, p.ldl = x.data_ptr(), Cc, logits.data_ptr(), logits.shape[-1]
+    p.dy, p.lddy, p.dx, p.lddx, p.dlogits, p.lddl = dy.data_ptr(), Cc, dx.data_ptr(), Cc, dl.data_ptr(), logits.shape[-1]
+    p.T, p.B, p.C, p.H, p.K, p.dtype = T, B, Cc, H, K, _code(x)
+    _lib.check(_lib.lib().tnt_dynconv_bwd(C.byref(p), _st()), 'tnt_dynconv_bwd')
+    return dx, dl
+
+
+def dynconv_step(x, logits, ring, pos, H, K):
+    """x [B,C], logits [B,H*K], ring [(K-1),B,C] (updated in place), pos int32[1] device counter."""
+    x, logits = _cuda(x).contiguous(), logits.contiguous()
+    B, Cc = x.shape
+    y = torch.empty_like(x)
+    p = _lib.DynconvStepParams()
+    p.x, p.ldx, p.logits, p.ldl, p.y, p.ldy = x.data_ptr(), Cc, logits.data_ptr(), logits.shape[-1], y.data_ptr(), Cc
+    p.ring, p.pos = ring.data_ptr(), pos.data_ptr()
+    p.B, p.C, p.H, p.K, p.dtype = B, Cc, H, K, _code(x)
+    _lib.check(_lib.lib().tnt_dynconv_step(C.byref(p), _st()), 'tnt_dynconv_step')
+    return y
+
+
+def layernorm(x, gamma, beta, eps=1e-5, variant=0):
+    x = _cuda(x).contiguous()
+    Cc = x.shape[-1]
+    y = torch.empty_like(x)
+    p = _lib.LayernormParams()
+    p.x, p.ldx, p.y, p.ldy = x.data_ptr(), Cc, y.data_ptr(), Cc
+    gamma, beta = gamma.float().contiguous(), beta.float().contiguous()
+    p.gamma, p.beta = gamma.data_ptr(), beta.data_ptr()
+    p.rows, p.C, p.groups, p.variant, p.eps, p.dtype = x.numel() // Cc, Cc, 1, variant, eps, _code(x)
+    _lib.check(_lib.lib().tnt_layernorm_fwd(C.byref(p), _st()), 'tnt_layernorm_fwd')
+    return y
+
+
+def layernorm_bwd(x, dy, gamma, eps=1e-5):
+    x, dy = _cuda(x).contiguous(), dy.contiguous()
+    Cc = x.shape[-1]
+    dx = torch.empty_like(x)
+    gamma = gamma.float().contiguous()
+    dg = torch.zeros(Cc, dtype=torch.float32, device=x.device)
+    db = torch.zeros(Cc, dtype=torch.float32, device=x.device)
+    p = _lib.LayernormBwdParams()
+    p.x, p.ldx, p.dy, p.lddy, p.dx, p.lddx = x.data_ptr(), Cc, dy.data_ptr(), Cc, dx.data_ptr(), Cc
+    p.gamma, p.dgamma, p.dbeta = gamma.data_ptr(), dg.data_ptr(), db.data_ptr()
+    p.rows, p.C, p.eps, p.dtype = x.numel() // Cc, Cc, eps, _code(x)
+    _lib.check(_lib.lib().tnt_layernorm_bwd(C.byref(p), _st()), 'tnt_layernorm_bwd')
+    return dx, dg, db
+
+
+def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=None, need_weights=False):
+    """q [T,B,E], k/v [S,B,E] (projected) -> out [T,B,E] (+ head-averaged weights [B,T,S+n_extra]).
+    pad_mask [B,S] bool True=pad (tell);  v2_mask [B,1|T,S] 'visible' mask (final*), 0 -> -1e9."""
+    q, k, v = _cuda(q).contiguous(), k.contiguous(), v.contiguous()
+    T, B, E = q.shape
+    S = k.shape[0]
+    out = torch.empty_like(q)
+    p = _lib.XattnParams()
+    p.q, p.q_stride_t, p.q_stride_b = q.data_ptr(), B * E, E
+    p.k, p.k_stride_s, p.k_stride_b = k.data_ptr(), B * E, E
+    p.v, p.v_stride_s, p.v_stride_b = v.data_ptr(), B * E, E
+    p.out, p.o_stride_t, p.o_stride_b = out.data_ptr(), B * E, E
+    keep = []
+    n_extra = 0
+    if bias_k is not None:
+        bk, bv = bias_k.float().contiguous().view(-1), bias_v.float().contiguous().view(-1)
+        keep += [bk, bv]
+        p.bias_k, p.bias_v, n_extra = bk.data_ptr(), bv.data_ptr(), 2
+    p.mask_mode = MASK_NONE
+    if pad_mask is not None:
+        m = pad_mask.to(torch.bool).contiguous()
+        keep.append(m)
+        p.mask, p.m_stride_b, p.m_stride_t, p.mask_mode = m.data_ptr(), S, 0, MASK_KEY_PADDING
+    elif v2_mask is not None:
+        m = v2_mask.to(torch.bool).expand(B, v2_mask.shape[1], S).contiguous()
+        keep.append(m)
+        p.mask, p.m_stride_b, p.mask_mode = m.data_ptr(), m.shape[1] * S, MASK_V2
+        p.m_stride_t = S if m.shape[1] > 1 else 0
+    w = None
+    if need_weights:
+        w = torch.empty(B, T, S + n_extra, dtype=torch.float32, device=q.device)
+        p.weights = w.data_ptr()
+    p.B, p.T, p.S, p.H, p.D, p.n_extra, p.scale, p.dtype = B, T, S, H, E // H, n_extra, scale, _code(q)
+    _lib.check(_lib.lib().tnt_xattn_fwd(C.byref(p), _st()), 'tnt_xattn_fwd')
+    return out, w
+
+
+def lse(x, w, bias=None, target=None):
+    """Row statistics of z = x @ w^T (+bias) without materialising z:
+    returns (max, sumexp, argmax, target_logit) as tensors [M]."""
+    x, w = _cuda(x).contiguous(), w.contiguous()
+    M, K = x.shape
+    N = w.shape[0]
+    L = _lib.lib()
+    ws = torch.empty(L.tnt_lse_workspace_bytes(M, N, _code(x)) + 256, dtype=torch.uint8, device=x.device)
+    stats = torch.empty(M, 4, dtype=torch.float32, device=x.device)
+    p = _lib.LseParams()
+    p.x, p.ldx, p.w, p.ldw = x.data_ptr(), K, w.data_ptr(), K
+    p.bias = bias.data_ptr() if bias is not None else None
+    tg = target.to(torch.int32).contiguous() if target is not None else None
+    p.target = tg.data_ptr() if tg is not None else None
+    p.stats, p.workspace, p.workspace_bytes = stats.data_ptr(), ws.data_ptr(), ws.numel()
+    p.M, p.n_cols, p.K, p.dtype = M, N, K, _code(x)
+    _lib.check(L.tnt_lse_fwd(C.byref(p), _st()), 'tnt_lse_fwd')
+    return stats[:, 0], stats[:, 1], stats[:, 2].contiguous().view(torch.int32), stats[:, 3]

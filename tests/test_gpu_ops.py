@@ -1,0 +1,223 @@
+"""GPU parity tests of the fine-grained C-ABI ops against the oracle (oracle/restate.py) and the golden
+fixtures frozen from the unmodified reference.  Tolerances: fp32 1e-4 relative, bf16 2e-2 (north_star)."""
+import os
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import restate as O
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), 'golden')
+TOL = {torch.float32: 1e-4, torch.bfloat16: 2e-2}
+
+
+def rel_err(a, b):
+    a, b = a.float().cpu(), b.float().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+
+
+@pytest.fixture(scope='module')
+def ops():
+    from news_image_caption_b200 import build, _lib, ops as o
+    build.build()
+    _lib.require_device()
+    return o
+
+
+# ----------------------------------------------------------------------------- GEMM
+@pytest.mark.parametrize('M,N,K', [(128, 256, 64), (200, 1000, 1024), (2048, 2048, 1024), (77, 48, 32),
+                                   (256, 5002, 1024), (3136, 8192, 2048), (1, 496, 1024)])
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float32])
+def test_linear(ops, M, N, K, dtype):
+    g = torch.Generator().manual_seed(M + N + K)
+    a = torch.randn(M, K, generator=g).to(dtype)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(dtype)
+    b = torch.randn(N, generator=g)
+    ref = a.double() @ w.double().t() + b.double()          # plain torch reference of the same op
+    out = ops.linear(a.cuda(), w.cuda(), b.cuda())
+    torch.cuda.synchronize()
+    assert rel_err(out, ref) < (1e-5 if dtype == torch.float32 else 8e-3)
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float32])
+def test_linear_epilogues(ops, dtype):
+    from news_image_caption_b200 import _lib
+    g = torch.Generator().manual_seed(3)
+    M, N, K = 300, 512, 256
+    a = torch.randn(M, K, generator=g).to(dtype)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(dtype)
+    b = torch.randn(N, generator=g)
+    r = torch.randn(M, N, generator=g).to(dtype)
+    z = a.double() @ w.double().t() + b.double()
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    assert rel_err(ops.linear(a.cuda(), w.cuda(), b.cuda(), _lib.EPI_RELU), z.relu()) < tol
+    assert rel_err(ops.linear(a.cuda(), w.cuda(), b.cuda(), _lib.EPI_RESIDUAL, residual=r.cuda()), z + r.double()) < tol
+    # GLU: interleave rows with the library's own fold so the pairing convention is what is tested
+    wi = ops.wn_fold(w.float().cuda(), None, glu_interleave=True, dtype=dtype)
+    bi = ops.glu_interleave_bias(b.cuda())
+    glu = F.glu(z, dim=-1)
+    assert rel_err(ops.linear(a.cuda(), wi, bi, _lib.EPI_GLU), glu) < tol
+
+
+def test_tc_matches_simt(ops):
+    """tcgen05 GEMM against the library's own fp32-accumulating SIMT kernel on identical bf16 inputs."""
+    from news_image_caption_b200 import _lib
+    g = torch.Generator().manual_seed(5)
+    a = torch.randn(513, 1024, generator=g).bfloat16().cuda()
+    w = (torch.randn(777, 1024, generator=g) / 32).bfloat16().cuda()
+    tc = ops.linear(a, w, out_dtype=torch.float32)
+    _lib.lib().tnt_debug_force_simt_gemm(1)
+    try:
+        sm = ops.linear(a, w, out_dtype=torch.float32)
+    finally:
+        _lib.lib().tnt_debug_force_simt_gemm(0)
+    assert rel_err(tc, sm) < 1e-5
+
+
+def test_wn_fold(ops):
+    g = torch.Generator().manual_seed(2)
+    v, gg = torch.randn(64, 40, generator=g), torch.randn(64, 1, generator=g)
+    assert rel_err(ops.wn_fold(v.cuda(), gg.cuda()), O.fold_weight_norm(gg, v)) < 1e-6
+
+
+# ----------------------------------------------------------------------------- DynamicConv
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_dynconv_golden(ops, dtype):
+    for c in torch.load(os.path.join(G, 'dynconv_cases.pt'), weights_only=False):
+        x = c['x'].to(dtype)
+        logits = F.linear(x.float(), c['w']).to(dtype)           # the tap GEMM is tested separately
+        y = ops.dynconv(x.cuda(), logits.cuda(), c['H'], c['K'])
+        if dtype == torch.float32:
+            assert rel_err(y, c['y']) < 1e-5, (c['T'], c['K'])
+        else:
+            w = F.softmax(logits.float().view(c['T'], c['B'], c['H'], c['K']), -1)
+            xp = F.pad(x.float(), (0, 0, 0, 0, c['K'] - 1, 0)).unfold(0, c['K'], 1)
+            ref = torch.einsum('tbhrk,tbhk->tbhr', xp.reshape(c['T'], c['B'], c['H'], -1, c['K']), w).reshape(x.shape)
+            assert rel_err(y, ref) < 1e-2
+
+
+def test_dynconv_full_size_and_step(ops):
+    """T=32, B=8, C=1024, H=16, K=31 vs the oracle; incremental ring-buffer steps == full sequence."""
+    g = torch.Generator().manual_seed(9)
+    T, B, Cc, H, K = 32, 8, 1024, 16, 31
+    x = torch.randn(T, B, Cc, generator=g)
+    wt = torch.randn(H * K, Cc, generator=g) / 32
+    ref = O.dynamic_conv(x, wt, H, K)
+    logits = F.linear(x, wt)
+    y = ops.dynconv(x.cuda(), logits.cuda(), H, K)
+    assert rel_err(y, ref) < 1e-5
+    ring = torch.zeros(K - 1, B, Cc, device='cuda')
+    pos = torch.zeros(1, dtype=torch.int32, device='cuda')
+    ys = []
+    for t in range(T):
+        ys.append(ops.dynconv_step(x[t].cuda(), logits[t].cuda(), ring, pos, H, K))
+        pos += 1
+    assert rel_err(torch.stack(ys), ref) < 1e-5
+    # history form (dynamic.py:95-99): last K-1 inputs + 3 new steps
+    y2 = ops.dynconv(x[20:23].cuda(), logits[20:23].cuda(), H, K, hist=x[:20][-(K - 1):].cuda())
+    assert rel_err(y2, ref[20:23]) < 1e-5
+
+
+def test_dynconv_backward(ops):
+    g = torch.Generator().manual_seed(10)
+    T, B, Cc, H, K = 12, 3, 64, 4, 7
+    x = torch.randn(T, B, Cc, generator=g, requires_grad=True)
+    logits = torch.randn(T, B, H * K, generator=g, requires_grad=True)
+    w = F.softmax(logits.view(T, B, H, K), -1)
+    xp = F.pad(x, (0, 0, 0, 0, K - 1, 0)).unfold(0, K, 1)
+    y = torch.einsum('tbhrk,tbhk->tbhr', xp.reshape(T, B, H, Cc // H, K), w).reshape(T, B, Cc)
+    dy = torch.randn(T, B, Cc, generator=g)
+    gx, gl = torch.autograd.grad(y, [x, logits], dy)
+    dx, dl = ops.dynconv_bwd(x.detach().cuda(), logits.detach().cuda(), dy.cuda(), H, K)
+    assert rel_err(dx, gx) < 1e-5
+    assert rel_err(dl, gl) < 1e-5
+
+
+# ----------------------------------------------------------------------------- LayerNorm
+def test_layernorm(ops):
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(70, 1024, generator=g) * 3 + 1
+    gm, bt = torch.randn(1024, generator=g), torch.randn(1024, generator=g)
+    ref = F.layer_norm(x, (1024,), gm, bt)
+    assert rel_err(ops.layernorm(x.cuda(), gm.cuda(), bt.cuda()), ref) < 1e-5
+    assert rel_err(ops.layernorm(x.bfloat16().cuda(), gm.cuda(), bt.cuda()), ref) < 2e-2
+    v2 = O.v2_layer_norm(x, gm, bt)
+    assert rel_err(ops.layernorm(x.cuda(), gm.cuda(), bt.cuda(), eps=1e-6, variant=1), v2) < 1e-5
+    xr = x.clone().requires_grad_(True)
+    dy = torch.randn(70, 1024, generator=g)
+    gmr, btr = gm.clone().requires_grad_(True), bt.clone().requires_grad_(True)
+    gx, gg, gb = torch.autograd.grad(F.layer_norm(xr, (1024,), gmr, btr), [xr, gmr, btr], dy)
+    dx, dg, db = ops.layernorm_bwd(x.cuda(), dy.cuda(), gm.cuda())
+    assert rel_err(dx, gx) < 1e-4 and rel_err(dg, gg) < 1e-4 and rel_err(db, gb) < 1e-4
+
+
+# ----------------------------------------------------------------------------- attention
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_xattn_golden(ops, dtype):
+    for c in torch.load(os.path.join(G, 'mha_cases.pt'), weights_only=False):
+        sd, E, H = c['state_dict'], c['E'], c['H']
+        wq, wk, wv, bq, bk, bv = O.mha_params(sd, '', E)
+        q = F.linear(c['query'], wq, bq).to(dtype)
+        k = F.linear(c['memory'], wk, bk).to(dtype)
+        v = F.linear(c['memory'], wv, bv).to(dtype)
+        o, w = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, (E // H) ** -0.5, pad_mask=c['mask'].cuda(),
+                         bias_k=sd['bias_k'].cuda(), bias_v=sd['bias_v'].cuda(), need_weights=True)
+        out = F.linear(o.float().cpu(), sd['out_proj.weight'], sd['out_proj.bias'])
+        assert rel_err(out, c['out']) < TOL[dtype]
+        assert rel_err(w, c['weights']) < TOL[dtype]
+
+
+def test_xattn_full_size(ops):
+    """T=32, B=3, H=16, D=64, S=512 with ragged padding, vs the oracle's attention core."""
+    g = torch.Generator().manual_seed(6)
+    T, B, E, H, S = 32, 3, 1024, 16, 512
+    q, k, v = (torch.randn(n, B, E, generator=g) for n in (T, S, S))
+    bk, bv = torch.randn(1, 1, E, generator=g), torch.randn(1, 1, E, generator=g)
+    n = torch.tensor([512, 130, 0])
+    mask = torch.arange(S)[None] >= n[:, None]
+    sd = {'in_proj_bias': torch.zeros(3 * E), 'in_proj_weight': torch.eye(E).repeat(3, 1), 'bias_k': bk, 'bias_v': bv,
+          'out_proj.weight': torch.eye(E), 'out_proj.bias': torch.zeros(E)}
+    kk = torch.cat([k, bk.expand(1, B, E), torch.zeros(1, B, E)])
+    vv = torch.cat([v, bv.expand(1, B, E), torch.zeros(1, B, E)])
+    ref, wref = O.mha_attend(q, kk, vv, mask, sd, '', H)
+    o, w = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, 64 ** -0.5, pad_mask=mask.cuda(), bias_k=bk.cuda(),
+                     bias_v=bv.cuda(), need_weights=True)
+    assert rel_err(o, ref) < 1e-4 and rel_err(w, wref) < 1e-4
+    ob, _ = ops.xattn(q.bfloat16().cuda(), k.bfloat16().cuda(), v.bfloat16().cuda(), H, 64 ** -0.5,
+                      pad_mask=mask.cuda(), bias_k=bk.cuda(), bias_v=bv.cuda())
+    assert rel_err(ob, ref) < 2e-2
+
+
+def test_xattn_v2_causal(ops):
+    """final*/transformer_v2 attention(): mask == 0 -> -1e9, causal self-attention, d_k = 128."""
+    g = torch.Generator().manual_seed(8)
+    B, T, d, h = 2, 9, 256, 2
+    x = torch.randn(B, T, d, generator=g)
+    sd = {'linears.0.weight': torch.eye(d), 'linears.0.bias': torch.zeros(d), 'linears.1.weight': torch.eye(d),
+          'linears.1.bias': torch.zeros(d), 'linear_kv.0.weight': torch.eye(d), 'linear_kv.0.bias': torch.zeros(d),
+          'linear_kv.1.weight': torch.eye(d), 'linear_kv.1.bias': torch.zeros(d)}
+    tm = O.v2_subsequent_mask(T)
+    ref = O.v2_mha(x, x, tm, sd, '', h)
+    xt = x.transpose(0, 1).contiguous().cuda()
+    o, _ = ops.xattn(xt, xt, xt, h, (d // h) ** -0.5, v2_mask=tm.cuda())
+    assert rel_err(o.transpose(0, 1), ref) < 1e-4
+
+
+# ----------------------------------------------------------------------------- LSE head
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_lse(ops, dtype):
+    g = torch.Generator().manual_seed(12)
+    M, N, K = 300, 5002, 256
+    x = torch.randn(M, K, generator=g).to(dtype)
+    w = (torch.randn(N, K, generator=g) / 8).to(dtype)
+    tgt = torch.randint(0, N, (M,), generator=g)
+    z = x.double() @ w.double().t()
+    m, s, arg, tz = ops.lse(x.cuda(), w.cuda(), target=tgt.cuda())
+    lse = (m.double() + s.double().log()).cpu()
+    tol = 1e-5 if dtype == torch.float32 else 1e-3
+    assert ((lse - torch.logsumexp(z, 1)).abs().max() / lse.abs().max()).item() < tol
+    assert rel_err(tz, z.gather(1, tgt[:, None])[:, 0]) < (1e-5 if dtype == torch.float32 else 1e-2)
+    if dtype == torch.float32:
+        assert torch.equal(arg.cpu().long(), z.argmax(1))
