@@ -200,6 +200,7 @@ typedef struct {
   int n_extra, mask_mode;
   float scale;
   int dtype;
+  int mask_S;         /* the mask covers keys [0, mask_S); 0 = all S (trailing k/v rows are then never masked) */
 } tnt_xattn_params;
 int tnt_xattn_fwd(const tnt_xattn_params* p, tnt_stream stream);
 

@@ -62,7 +62,7 @@ class XattnParams(C.Structure):
                 ('k_stride_b', i64), ('v', vp), ('v_stride_s', i64), ('v_stride_b', i64), ('out', vp),
                 ('o_stride_t', i64), ('o_stride_b', i64), ('mask', vp), ('m_stride_b', i64), ('m_stride_t', i64),
                 ('bias_k', vp), ('bias_v', vp), ('weights', vp), ('B', i32), ('T', i32), ('S', i32), ('H', i32),
-                ('D', i32), ('n_extra', i32), ('mask_mode', i32), ('scale', f32), ('dtype', i32)]
+                ('D', i32), ('n_extra', i32), ('mask_mode', i32), ('scale', f32), ('dtype', i32), ('mask_S', i32)]
 
 
 class LseParams(C.Structure):
@@ -117,6 +117,7 @@ _SIGS = {
     'tnt_decoder_score_host_staging_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
     'tnt_decoder_score_host': (i32, [vp, vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp, C.c_size_t, vp]),
     'tnt_debug_force_simt_gemm': (None, [i32]),
+    'tnt_debug_force_simt_attention': (None, [i32]),
 }
 
 _lib = None

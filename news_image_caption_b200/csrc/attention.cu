@@ -46,7 +46,8 @@ __device__ __forceinline__ void load_kv_tile(const tnt_xattn_params& p, const T*
 // scores of this lane's two keys (lane, lane+32 of the tile) against the warp's kQW queries, masks applied
 __device__ __forceinline__ void tile_scores(const tnt_xattn_params& p, const float* qs, const float* ks, int b,
                                             int t0, int qw, int nq, int key0, int lane, float (&s)[kQW][2]) {
-  const int D = p.D, S = p.S, S2 = p.S + p.n_extra;
+  const int D = p.D, S2 = p.S + p.n_extra;
+  const int S = p.mask_S > 0 ? min(p.mask_S, p.S) : p.S;     // keys the mask covers
 #pragma unroll
   for (int qi = 0; qi < kQW; ++qi) s[qi][0] = s[qi][1] = 0.f;
   const float* k0 = ks + lane * (D + 1);
@@ -233,9 +234,17 @@ int xattn_check(const tnt_xattn_params* p) {
   return TNT_OK;
 }
 
-int xattn_fwd_dispatch(const tnt_xattn_params* p, cudaStream_t st) { return xattn_fwd_simt(p, st); }
+bool xattn_tc_supported(const tnt_xattn_params* p);
+int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st);
+static bool g_force_simt_attn = false;
+int xattn_fwd_dispatch(const tnt_xattn_params* p, cudaStream_t st) {
+  if (!g_force_simt_attn && xattn_tc_supported(p)) return xattn_fwd_tc(p, st);
+  return xattn_fwd_simt(p, st);
+}
 
 }  // namespace tnt
+
+extern "C" void tnt_debug_force_simt_attention(int on) { tnt::g_force_simt_attn = on != 0; }
 
 extern "C" int tnt_xattn_fwd(const tnt_xattn_params* p, tnt_stream stream) {
   using namespace tnt;

@@ -1,0 +1,336 @@
+// tcgen05 / TMEM / TMA multi-head attention forward (kernel group 2), bf16 inputs, head dim 64.
+// Reference math: ttl/tell/modules/attention/multi_head.py:376-477 (scaled QK^T, key-padding mask, fp32
+// softmax, PV).  The extra bias_k / zero rows are ordinary k/v rows here (the engine materialises them
+// once per batch, engine_fwd.cu), the mask covers the first `mask_S` keys only.
+//
+// One work item = (batch row b, PAIR of heads, tile of <= 32 queries); persistent CTAs, 10 warps:
+//   warp 0      TMA producer: Q pair, then 128-key K tiles and V tiles (128B swizzle) through mbarrier rings
+//   warp 1      one thread issues tcgen05.mma:
+//                 S^T[keys, q] = K_h[keys, 64] . Q_h[q, 64]^T   (M=128 keys, N=32 queries, per head)
+//                 O^T[(h,d), (h',q)] += V[(h,d), keys] . P[keys, (h',q)]   (M=128 = 2 heads x 64 dims, N=64)
+//               -> every score tile of the item stays in TMEM (<= 7 tiles x 64 columns), O^T in 64 more
+//   warps 2-9   softmax: lane = key, exact two-pass softmax in fp32 straight out of TMEM (column max with
+//               redux.sync + one cross-warp exchange), P written to smem as the bf16 MN-major B operand,
+//               epilogue: O^T * 1/l -> global (lanes = consecutive channels, coalesced)
+// Zero padding waste in M for the score MMAs (keys fill M), 2x waste (cross-head blocks) in the PV MMAs.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace tnt {
+
+int make_tmap_bf16_3d(CUtensorMap* tm, const void* base, long d0, long d1, long d2, long stride1, long stride2,
+                      int box0, int box1, int box2);
+
+namespace atc {
+constexpr int kThreads = 320;
+constexpr int TQ = 32, TKEYS = 128, D = 64;
+constexpr int KS = 3, VS = 2, PS = 2;
+constexpr int Q_BYTES = 2 * TQ * 128;             // two heads
+constexpr int KV_STAGE = 2 * TKEYS * 128;         // two heads x 128 keys x 128 B
+constexpr int P_STAGE = TKEYS * 128;              // 128 keys x 64 (h,q) bf16
+constexpr int MAX_TILES = 7;
+constexpr uint32_t O_COL = 448;
+constexpr int SMEM_BYTES = Q_BYTES + KS * KV_STAGE + VS * KV_STAGE + PS * P_STAGE + 4096 + 2048;
+
+struct Args {
+  const uint8_t* mask; long m_stride_b;
+  void* out; long o_stride_t, o_stride_b;
+  int B, T, S, H, mask_S;
+  float scale_log2e;
+  int n_items, n_qt, n_tiles;
+};
+
+struct Bars {
+  uint64_t q_full, q_empty, s_ready, s_empty, o_ready, o_empty;
+  uint64_t k_full[KS], k_empty[KS], v_full[VS], v_empty[VS], p_ready[PS], p_empty[PS];
+  uint32_t tmem;
+};
+
+__device__ __forceinline__ float redux_max(float v) {
+  float r;
+  asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+}
+__device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+__global__ void __launch_bounds__(kThreads, 1)
+xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                const __grid_constant__ CUtensorMap tmV, Args a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + Q_BYTES;
+  uint8_t* sV = sK + KS * KV_STAGE;
+  uint8_t* sP = sV + VS * KV_STAGE;
+  float* red = reinterpret_cast<float*>(sP + PS * P_STAGE);          // [2 heads][4 quadrants][32] x 2 (max, sum)
+  Bars* bar = reinterpret_cast<Bars*>(reinterpret_cast<uint8_t*>(red) + 4096);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles = a.n_tiles;
+
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tmap(&tmQ);
+    ptx::prefetch_tmap(&tmK);
+    ptx::prefetch_tmap(&tmV);
+    ptx::mbar_init(&bar->q_full, 1);
+    ptx::mbar_init(&bar->q_empty, 1);
+    ptx::mbar_init(&bar->s_ready, 1);
+    ptx::mbar_init(&bar->s_empty, 8);
+    ptx::mbar_init(&bar->o_ready, 1);
+    ptx::mbar_init(&bar->o_empty, 8);
+    for (int i = 0; i < KS; ++i) { ptx::mbar_init(&bar->k_full[i], 1); ptx::mbar_init(&bar->k_empty[i], 1); }
+    for (int i = 0; i < VS; ++i) { ptx::mbar_init(&bar->v_full[i], 1); ptx::mbar_init(&bar->v_empty[i], 1); }
+    for (int i = 0; i < PS; ++i) { ptx::mbar_init(&bar->p_ready[i], 8); ptx::mbar_init(&bar->p_empty[i], 1); }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc<512>(&bar->tmem);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = bar->tmem;
+  const int HP = a.H >> 1;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int ks = 0, vs = 0;
+      uint32_t kph = 0, vph = 0, it = 0;
+      for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
+        const int qt = item % a.n_qt, r = item / a.n_qt, hp = r % HP, b = r / HP;
+        const int c0 = hp * 2 * D;
+        ptx::mbar_wait(&bar->q_empty, (it & 1) ^ 1);
+        ptx::mbar_arrive_expect_tx(&bar->q_full, Q_BYTES);
+        ptx::tma_load_3d(sQ, &tmQ, &bar->q_full, c0, b, qt * TQ);
+        ptx::tma_load_3d(sQ + TQ * 128, &tmQ, &bar->q_full, c0 + D, b, qt * TQ);
+        for (int i = 0; i < n_tiles; ++i) {
+          ptx::mbar_wait(&bar->k_empty[ks], kph ^ 1);
+          ptx::mbar_arrive_expect_tx(&bar->k_full[ks], KV_STAGE);
+          ptx::tma_load_3d(sK + ks * KV_STAGE, &tmK, &bar->k_full[ks], c0, b, i * TKEYS);
+          ptx::tma_load_3d(sK + ks * KV_STAGE + TKEYS * 128, &tmK, &bar->k_full[ks], c0 + D, b, i * TKEYS);
+          if (++ks == KS) { ks = 0; kph ^= 1; }
+        }
+        for (int i = 0; i < n_tiles; ++i) {
+          ptx::mbar_wait(&bar->v_empty[vs], vph ^ 1);
+          ptx::mbar_arrive_expect_tx(&bar->v_full[vs], KV_STAGE);
+          ptx::tma_load_3d(sV + vs * KV_STAGE, &tmV, &bar->v_full[vs], c0, b, i * TKEYS);
+          ptx::tma_load_3d(sV + vs * KV_STAGE + TKEYS * 128, &tmV, &bar->v_full[vs], c0 + D, b, i * TKEYS);
+          if (++vs == VS) { vs = 0; vph ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc_qk = ptx::umma_idesc_bf16(128, TQ, 0, 0);
+      const uint32_t idesc_pv = ptx::umma_idesc_bf16(128, 2 * TQ, 1, 1);
+      int ks = 0, vs = 0, ps = 0;
+      uint32_t kph = 0, vph = 0, pph = 0, it = 0;
+      for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
+        const uint32_t par = it & 1;
+        ptx::mbar_wait(&bar->q_full, par);
+        ptx::mbar_wait(&bar->s_empty, par ^ 1);            // previous item's scores have been consumed
+        ptx::tc_fence_after();
+        const uint32_t q_addr = ptx::smem_u32(sQ);
+        for (int i = 0; i < n_tiles; ++i) {
+          ptx::mbar_wait(&bar->k_full[ks], kph);
+          ptx::tc_fence_after();
+          const uint32_t k_addr = ptx::smem_u32(sK + ks * KV_STAGE);
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+#pragma unroll
+            for (int k = 0; k < D / 16; ++k) {
+              const uint64_t ad = ptx::umma_smem_desc(k_addr + h * TKEYS * 128 + k * 32, 16, 1024);
+              const uint64_t bd = ptx::umma_smem_desc(q_addr + h * TQ * 128 + k * 32, 16, 1024);
+              ptx::umma_bf16_ss(tmem + i * 64 + h * 32, ad, bd, idesc_qk, k != 0);
+            }
+          }
+          ptx::umma_commit(&bar->k_empty[ks]);
+          if (++ks == KS) { ks = 0; kph ^= 1; }
+        }
+        ptx::umma_commit(&bar->q_empty);
+        ptx::umma_commit(&bar->s_ready);
+        ptx::mbar_wait(&bar->o_empty, par ^ 1);            // previous item's output has been read
+        ptx::tc_fence_after();
+        for (int i = 0; i < n_tiles; ++i) {
+          ptx::mbar_wait(&bar->v_full[vs], vph);
+          ptx::mbar_wait(&bar->p_ready[ps], pph);
+          ptx::tc_fence_after();
+          const uint32_t v_addr = ptx::smem_u32(sV + vs * KV_STAGE);
+          const uint32_t p_addr = ptx::smem_u32(sP + ps * P_STAGE);
+#pragma unroll
+          for (int k = 0; k < TKEYS / 16; ++k) {
+            // A = V^T: MN-major, two 64-channel atoms (the two heads) TKEYS*128 B apart, 8-key groups 1024 B apart
+            const uint64_t ad = ptx::umma_smem_desc(v_addr + k * 2048, TKEYS * 128, 1024);
+            const uint64_t bd = ptx::umma_smem_desc(p_addr + k * 2048, 16, 1024);
+            ptx::umma_bf16_ss(tmem + O_COL, ad, bd, idesc_pv, (i | k) != 0);
+          }
+          ptx::umma_commit(&bar->v_empty[vs]);
+          ptx::umma_commit(&bar->p_empty[ps]);
+          if (++vs == VS) { vs = 0; vph ^= 1; }
+          if (++ps == PS) { ps = 0; pph ^= 1; }
+        }
+        ptx::umma_commit(&bar->o_ready);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------------ softmax + epilogue warps
+    const int quad = warp & 3;                 // TMEM lane quadrant
+    const int hd = (warp - 2) >> 2;            // which head's 32 score columns this warp owns
+    const uint32_t lane_base = static_cast<uint32_t>(quad * 32) << 16;
+    float* red_max = red + (hd * 4 + quad) * 32;
+    float* red_sum = red + 256 + (hd * 4 + quad) * 32;
+    int ps = 0;
+    uint32_t pph = 0, it = 0;
+    for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
+      const uint32_t par = it & 1;
+      const int qt = item % a.n_qt, r = item / a.n_qt, hp = r % HP, b = r / HP;
+      // validity of this lane's key in every tile (key-padding mask: multi_head.py:441-449)
+      uint32_t valid = 0;
+      for (int i = 0; i < n_tiles; ++i) {
+        const int key = i * TKEYS + quad * 32 + lane;
+        bool ok = key < a.S;
+        if (ok && a.mask && key < a.mask_S) ok = a.mask[static_cast<long>(b) * a.m_stride_b + key] == 0;
+        valid |= static_cast<uint32_t>(ok) << i;
+      }
+      ptx::mbar_wait(&bar->s_ready, par);
+      ptx::tc_fence_after();
+      // ---- pass 1: column maxima over the keys
+      float mx[32];
+#pragma unroll
+      for (int c = 0; c < 32; ++c) mx[c] = -INFINITY;
+      for (int i = 0; i < n_tiles; ++i) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tmem + lane_base + i * 64 + hd * 32, v);
+        ptx::tmem_ld_wait();
+        if ((valid >> i) & 1) {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) mx[c] = fmaxf(mx[c], __uint_as_float(v[c]));
+        }
+      }
+      float mine = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        const float w = redux_max(mx[c]);
+        if (lane == c) mine = w;
+      }
+      red_max[lane] = mine;
+      named_bar(1 + hd, 128);
+      {
+        const float* rm = red + hd * 128;
+        const float m4 = fmaxf(fmaxf(rm[lane], rm[32 + lane]), fmaxf(rm[64 + lane], rm[96 + lane]));
+        const float ms = (m4 == -INFINITY) ? 0.f : m4;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) mx[c] = __shfl_sync(0xffffffffu, ms, c) * a.scale_log2e;
+      }
+      // ---- pass 2: probabilities -> smem (bf16, MN-major B operand), running column sums
+      float ls[32];
+#pragma unroll
+      for (int c = 0; c < 32; ++c) ls[c] = 0.f;
+      for (int i = 0; i < n_tiles; ++i) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tmem + lane_base + i * 64 + hd * 32, v);
+        ptx::tmem_ld_wait();
+        const bool ok = (valid >> i) & 1;
+        uint32_t pk[16];
+#pragma unroll
+        for (int c = 0; c < 32; c += 2) {
+          float p0 = ok ? exp2f(fmaf(__uint_as_float(v[c]), a.scale_log2e, -mx[c])) : 0.f;
+          float p1 = ok ? exp2f(fmaf(__uint_as_float(v[c + 1]), a.scale_log2e, -mx[c + 1])) : 0.f;
+          ls[c] += p0;
+          ls[c + 1] += p1;
+          pk[c >> 1] = pack_bf16x2(p0, p1);
+        }
+        ptx::mbar_wait(&bar->p_empty[ps], pph ^ 1);
+        const int row = quad * 32 + lane;
+        uint8_t* prow = sP + ps * P_STAGE + row * 128;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int chunk = (hd * 4 + j) ^ (row & 7);             // 128-byte swizzle
+          *reinterpret_cast<uint4*>(prow + chunk * 16) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+        }
+        ptx::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&bar->p_ready[ps]);
+        if (++ps == PS) { ps = 0; pph ^= 1; }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&bar->s_empty);        // score columns may be overwritten
+      // column sums across the warp, then across the 4 quadrant warps of this head
+      float mysum = 0.f;
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        const float w = warp_sum(ls[c]);
+        if (lane == c) mysum = w;
+      }
+      red_sum[lane] = mysum;
+      named_bar(3, 256);                 // the epilogue reads the sums of BOTH head groups
+      // ---- epilogue: O^T rows of this quadrant belong to head (quad / 2); this warp takes 16 queries
+      const int oh = quad >> 1;
+      const int q0 = hd * 16;
+      ptx::mbar_wait(&bar->o_ready, par);
+      ptx::tc_fence_after();
+      uint32_t o[16];
+      ptx::tmem_ld_32x16(tmem + lane_base + O_COL + oh * 32 + q0, o);
+      ptx::tmem_ld_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&bar->o_empty);
+      const float* rs = red + 256 + oh * 128;
+      const int dch = (quad & 1) * 32 + lane;                     // channel inside the head
+      bf16* out = reinterpret_cast<bf16*>(a.out) + static_cast<long>(b) * a.o_stride_b + (hp * 2 + oh) * D + dch;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int q = q0 + j, t = qt * TQ + q;
+        const float l = rs[q] + rs[32 + q] + rs[64 + q] + rs[96 + q];
+        if (t < a.T) out[static_cast<long>(t) * a.o_stride_t] = __float2bfloat16_rn(l > 0.f ? __uint_as_float(o[j]) / l : 0.f);
+      }
+      named_bar(3, 256);                 // red[] is rewritten by the next item only after everyone has read it
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) ptx::tmem_dealloc<512>(tmem);
+}
+}  // namespace atc
+
+bool xattn_tc_supported(const tnt_xattn_params* p) {
+  if (p->dtype != TNT_BF16 || p->D != 64 || (p->H & 1) || p->n_extra != 0 || p->weights) return false;
+  if (p->mask_mode != TNT_MASK_NONE && p->mask_mode != TNT_MASK_KEY_PADDING) return false;
+  if (p->S < 1 || p->S > atc::MAX_TILES * atc::TKEYS) return false;
+  const long strides = p->q_stride_t | p->q_stride_b | p->k_stride_s | p->k_stride_b | p->v_stride_s | p->v_stride_b;
+  return (strides % 8) == 0 && aligned16(p->q) && aligned16(p->k) && aligned16(p->v);
+}
+
+int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st) {
+  CUtensorMap tmQ, tmK, tmV;
+  const int E = p->H * p->D;
+  TNT_TRY(make_tmap_bf16_3d(&tmQ, p->q, E, p->B, p->T, p->q_stride_b, p->q_stride_t, 64, 1, atc::TQ));
+  TNT_TRY(make_tmap_bf16_3d(&tmK, p->k, E, p->B, p->S, p->k_stride_b, p->k_stride_s, 64, 1, atc::TKEYS));
+  TNT_TRY(make_tmap_bf16_3d(&tmV, p->v, E, p->B, p->S, p->v_stride_b, p->v_stride_s, 64, 1, atc::TKEYS));
+  atc::Args a;
+  a.mask = p->mask_mode == TNT_MASK_KEY_PADDING ? p->mask : nullptr;
+  a.m_stride_b = p->m_stride_b;
+  a.out = p->out; a.o_stride_t = p->o_stride_t; a.o_stride_b = p->o_stride_b;
+  a.B = p->B; a.T = p->T; a.S = p->S; a.H = p->H;
+  a.mask_S = p->mask_S > 0 ? p->mask_S : p->S;
+  a.scale_log2e = p->scale * 1.4426950408889634f;
+  a.n_qt = (p->T + atc::TQ - 1) / atc::TQ;
+  a.n_items = p->B * (p->H / 2) * a.n_qt;
+  a.n_tiles = (p->S + atc::TKEYS - 1) / atc::TKEYS;
+  static bool attr = false;
+  if (!attr) {
+    TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
+    attr = true;
+  }
+  const int grid = std::min(a.n_items, num_sms());
+  atc::xattn_tc_kernel<<<grid, atc::kThreads, atc::SMEM_BYTES, st>>>(tmQ, tmK, tmV, a);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+}  // namespace tnt

@@ -47,6 +47,7 @@ struct tnt_decoder {
   std::vector<tnt::LayerW> layers;
   void* wkv[TNT_MAX_SOURCES] = {};     // [L*2d, source_dim]: per layer K rows then V rows
   float* bkv[TNT_MAX_SOURCES] = {};    // [L*2d]
+  float* kvrow[TNT_MAX_SOURCES] = {};  // [L*2d] the learned bias_k | bias_v row of every layer (extra key S)
   void* table = nullptr;               // [vocab, d] pre-projected, pre-scaled embedding
   float* pos_table = nullptr;          // [max_positions, d]
   tnt::AdaSoftmax ada;

@@ -32,6 +32,17 @@ int layernorm(const void* x, void* y, long ld, const float* g, const float* b, i
   p.transpose_T = tT; p.transpose_B = tB;
   return tnt_layernorm_fwd(&p, st);
 }
+// rows S and S+1 of a K/V buffer: the learned bias_k|bias_v row and the all-zero row that
+// add_bias_kv / add_zero_attn append to every source (multi_head.py:355-374, 416-427)
+template <typename T>
+__global__ void kv_extra_rows_kernel(T* kv, const float* row, int S, int B, int ld) {
+  const long n = static_cast<long>(B) * ld;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % ld);
+    kv[static_cast<long>(S) * n + i] = from_f<T>(row[c]);
+    kv[static_cast<long>(S + 1) * n + i] = from_f<T>(0.f);
+  }
+}
 }  // namespace
 
 FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool with_kv) {
@@ -50,7 +61,7 @@ FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool
   w.Q = take(N * ns * d * E); w.AO = take(N * ns * d * E); w.CAT = take(N * ns * d * E);
   w.F = take(N * c.ffn * E);
   for (size_t s = 0; s < ns; ++s)
-    w.kv[s] = with_kv ? take(static_cast<size_t>(S[s]) * B * c.n_layers * 2 * d * E) : nullptr;
+    w.kv[s] = with_kv ? take(static_cast<size_t>(S[s] + 2) * B * c.n_layers * 2 * d * E) : nullptr;
   w.total = off;
   return w;
 }
@@ -62,6 +73,12 @@ int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStre
   const tnt_decoder_config& c = D->cfg;
   const int ldkv = c.n_layers * 2 * c.d;
   for (int s = 0; s < c.n_sources; ++s) {
+    const int grid = std::min<long>((static_cast<long>(ctx->B) * ldkv + 255) / 256, 4L * num_sms());
+    if (c.dtype == TNT_BF16)
+      kv_extra_rows_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<bf16*>(w.kv[s]), D->kvrow[s], ctx->S[s], ctx->B, ldkv);
+    else
+      kv_extra_rows_kernel<float><<<grid, 256, 0, st>>>(static_cast<float*>(w.kv[s]), D->kvrow[s], ctx->S[s], ctx->B, ldkv);
+    TNT_LAUNCHED();
     if (ctx->S[s] == 0) continue;
     TNT_CHECK_ARG(ctx->memory[s], "decoder: context '%s' missing", c.source_names[s]);
     TNT_TRY(linear(ctx->memory[s], c.source_dim[s], D->wkv[s], c.source_dim[s], D->bkv[s], w.kv[s], ldkv,
@@ -109,12 +126,13 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     ap.o_stride_t = ap.q_stride_t; ap.o_stride_b = ap.q_stride_b;
     ap.mask = ctx->pad_mask[s]; ap.m_stride_b = ctx->S[s]; ap.m_stride_t = 0;
     ap.mask_mode = (ctx->pad_mask[s] && ctx->S[s] > 0) ? TNT_MASK_KEY_PADDING : TNT_MASK_NONE;
-    ap.bias_k = L.bias_k + s * d; ap.bias_v = L.bias_v + s * d;
     ap.weights = (attn_out && s == D->article_idx) ? attn_out : nullptr;
-    ap.B = B; ap.T = T; ap.S = ctx->S[s]; ap.H = H; ap.D = d / H; ap.n_extra = 2;
+    // the K/V buffer carries the 2 extra rows (project_kv), so they are plain keys the mask does not cover
+    ap.B = B; ap.T = T; ap.S = ctx->S[s] + 2; ap.H = H; ap.D = d / H; ap.n_extra = 0;
+    ap.mask_S = ctx->S[s];
+    if (ctx->S[s] == 0) ap.mask_mode = TNT_MASK_NONE;
     ap.scale = 1.0f / sqrtf(static_cast<float>(d / H));
     ap.dtype = dt;
-    if (ap.S == 0) { ap.k = ap.q; ap.v = ap.q; }           // no memory rows: only the 2 extra keys
     TNT_TRY(xattn_check(&ap));
     TNT_TRY(xattn_fwd_dispatch(&ap, st));
   }

@@ -55,6 +55,7 @@ size_t plan(tnt_decoder* D, char* base) {
   for (size_t s = 0; s < ns; ++s) {
     D->wkv[s] = a.take(L * 2 * d * c.source_dim[s] * E);
     D->bkv[s] = a.takef(L * 2 * d);
+    D->kvrow[s] = a.takef(L * 2 * d);
   }
   D->table = a.take(static_cast<size_t>(c.vocab) * d * E);
   D->pos_table = a.takef(static_cast<size_t>(c.max_positions) * d);
@@ -232,6 +233,8 @@ extern "C" int tnt_decoder_finalize(tnt_decoder* D, tnt_stream stream) {
       }
       L.vec_key(a + "bias_k", w.bias_k + s * d, d);
       L.vec_key(a + "bias_v", w.bias_v + s * d, d);
+      L.vec_key(a + "bias_k", D->kvrow[s] + static_cast<size_t>(l) * 2 * d, d);
+      L.vec_key(a + "bias_v", D->kvrow[s] + static_cast<size_t>(l) * 2 * d + d, d);
       if (const RawTensor* o = L.need(a + "out_proj.weight", static_cast<int64_t>(d) * d))
         L.matrix(o->data, static_cast<char*>(w.wo) + static_cast<size_t>(s) * d * d * E, d, d);
       L.vec_key(a + "out_proj.bias", w.bo + s * d, d);

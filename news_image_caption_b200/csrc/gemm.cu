@@ -140,13 +140,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
           for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
           if (EPI == EPI_LSE) {
+            if (g.bias) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              const int col = n0 + i;
-              if (col < g.N) {
-                const float z = acc[i] + (g.bias ? __ldg(g.bias + col) : 0.f);
-                if (col < g.n_lse) la.add(z, col, tgt);
-                else g.side[static_cast<long>(row) * g.side_ld + col - g.n_lse] = z;
+              for (int i = 0; i < 32; ++i)
+                if (n0 + i < g.N) acc[i] += __ldg(g.bias + n0 + i);
+            }
+            if (n0 + 32 <= g.n_lse) {                  // common case: whole chunk inside the cluster
+              la.add_chunk<32>(acc, n0, tgt);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                const int col = n0 + i;
+                if (col < g.N) {
+                  if (col < g.n_lse) la.add(acc[i], col, tgt);
+                  else g.side[static_cast<long>(row) * g.side_ld + col - g.n_lse] = acc[i];
+                }
               }
             }
           } else {
@@ -280,6 +288,29 @@ int make_tmap_bf16(CUtensorMap* tm, const void* base, long cols, long rows, long
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (%d): base %p cols %ld rows %ld ld %ld groups %ld gstride %ld", (int)r,
               base, cols, rows, ld, groups, group_stride);
+    return TNT_ERR_CUDA;
+  }
+  return TNT_OK;
+}
+
+// generic 3-D bf16 map, dims {d0 (contiguous), d1, d2}, element strides, 128-byte swizzle (box0 must be 64)
+int make_tmap_bf16_3d(CUtensorMap* tm, const void* base, long d0, long d1, long d2, long stride1, long stride2,
+                      int box0, int box1, int box2) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled entry point unavailable");
+    return TNT_ERR_CUDA;
+  }
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(d0), static_cast<cuuint64_t>(d1), static_cast<cuuint64_t>(d2)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(stride1) * 2, static_cast<cuuint64_t>(stride2) * 2};
+  cuuint32_t box[3] = {static_cast<cuuint32_t>(box0), static_cast<cuuint32_t>(box1), static_cast<cuuint32_t>(box2)};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(3d) failed (%d): dims %ld %ld %ld strides %ld %ld", (int)r, d0, d1, d2, stride1,
+              stride2);
     return TNT_ERR_CUDA;
   }
   return TNT_OK;

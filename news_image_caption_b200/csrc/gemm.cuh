@@ -110,6 +110,35 @@ struct LseAcc {
     }
     if (col == tgt) tz = z;
   }
+  // NC consecutive columns starting at col0, all valid: branch-free max/argmax pass, then ONE rescale
+  // of the running sum and NC exp2 (no data-dependent divergence inside the warp).
+  template <int NC>
+  __device__ __forceinline__ void add_chunk(const float (&z)[NC], int col0, int tgt) {
+    float cm = z[0];
+    int ca = 0;
+#pragma unroll
+    for (int i = 1; i < NC; ++i) {
+      const bool gt = z[i] > cm;
+      cm = gt ? z[i] : cm;
+      ca = gt ? i : ca;
+    }
+    if (cm > m) {
+      s *= exp2f((m - cm) * 1.4426950408889634f);
+      m = cm;
+      arg = col0 + ca;
+    }
+    const float mb = m * 1.4426950408889634f;
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < NC; ++i) acc += exp2f(fmaf(z[i], 1.4426950408889634f, -mb));
+    s += acc;
+    const int ti = tgt - col0;
+    if (ti >= 0 && ti < NC) {
+#pragma unroll
+      for (int i = 0; i < NC; ++i)
+        if (i == ti) tz = z[i];
+    }
+  }
   __device__ __forceinline__ void merge(float m2, float s2, int arg2, float tz2) {
     if (m2 > m || (m2 == m && arg2 >= 0 && (arg < 0 || arg2 < arg))) {
       s = s * ((m == -INFINITY) ? 0.f : __expf(m - m2)) + s2;

@@ -135,7 +135,7 @@ def layernorm_bwd(x, dy, gamma, eps=1e-5):
     return dx, dg, db
 
 
-def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=None, need_weights=False):
+def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=None, need_weights=False, mask_S=0):
     """q [T,B,E], k/v [S,B,E] (projected) -> out [T,B,E] (+ head-averaged weights [B,T,S+n_extra]).
     pad_mask [B,S] bool True=pad (tell);  v2_mask [B,1|T,S] 'visible' mask (final*), 0 -> -1e9."""
     q, k, v = _cuda(q).contiguous(), k.contiguous(), v.contiguous()
@@ -157,7 +157,8 @@ def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=No
     if pad_mask is not None:
         m = pad_mask.to(torch.bool).contiguous()
         keep.append(m)
-        p.mask, p.m_stride_b, p.m_stride_t, p.mask_mode = m.data_ptr(), S, 0, MASK_KEY_PADDING
+        p.mask, p.m_stride_b, p.m_stride_t, p.mask_mode = m.data_ptr(), m.shape[1], 0, MASK_KEY_PADDING
+        p.mask_S = mask_S
     elif v2_mask is not None:
         m = v2_mask.to(torch.bool).expand(B, v2_mask.shape[1], S).contiguous()
         keep.append(m)

@@ -190,6 +190,36 @@ def test_xattn_full_size(ops):
     assert rel_err(ob, ref) < 2e-2
 
 
+@pytest.mark.parametrize('T,B,S', [(32, 3, 514), (7, 2, 130), (1, 5, 51), (40, 2, 300)])
+def test_xattn_tcgen05(ops, T, B, S):
+    """tcgen05/TMEM attention kernel (bf16, D=64, extra rows materialised as ordinary keys, mask covering
+    only the first S-2 keys) vs a plain fp32 torch reference of the same op and vs the SIMT kernel."""
+    from news_image_caption_b200 import _lib
+    g = torch.Generator().manual_seed(T * 1000 + S)
+    E, H = 1024, 16
+    q = torch.randn(T, B, E, generator=g).bfloat16()
+    k = torch.randn(S, B, E, generator=g).bfloat16()
+    v = torch.randn(S, B, E, generator=g).bfloat16()
+    n = torch.randint(0, S - 1, (B,), generator=g)
+    n[0] = S - 2
+    mask = torch.arange(S - 2)[None] >= n[:, None]                      # [B, S-2]; last two keys never masked
+    full = torch.cat([mask, torch.zeros(B, 2, dtype=torch.bool)], 1)
+    qh = q.float().view(T, B, H, 64).permute(1, 2, 0, 3) * 0.125
+    kh = k.float().view(S, B, H, 64).permute(1, 2, 0, 3)
+    vh = v.float().view(S, B, H, 64).permute(1, 2, 0, 3)
+    s = (qh @ kh.transpose(-1, -2)).masked_fill(full[:, None, None, :], float('-inf'))
+    ref = (torch.softmax(s, -1) @ vh).permute(2, 0, 1, 3).reshape(T, B, E)
+    o, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, 0.125, pad_mask=mask.cuda(), mask_S=S - 2)
+    torch.cuda.synchronize()
+    assert rel_err(o, ref) < 2e-2
+    _lib.lib().tnt_debug_force_simt_attention(1)
+    try:
+        o2, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, 0.125, pad_mask=mask.cuda(), mask_S=S - 2)
+    finally:
+        _lib.lib().tnt_debug_force_simt_attention(0)
+    assert rel_err(o, o2) < 1.5e-2
+
+
 def test_xattn_v2_causal(ops):
     """final*/transformer_v2 attention(): mask == 0 -> -1e9, causal self-attention, d_k = 128."""
     g = torch.Generator().manual_seed(8)
