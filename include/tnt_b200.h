@@ -54,8 +54,15 @@ typedef enum {
   TNT_EPI_RELU = 1,      /* relu(acc + bias)                       decoder_flattened.py:338 */
   TNT_EPI_GLU = 2,       /* W rows pair-interleaved (a0,b0,a1,b1..): out[:, j] = a_j * sigmoid(b_j);
                             N counts the interleaved rows, C has N/2 columns.  decoder_flattened.py:284-286 */
-  TNT_EPI_RESIDUAL = 3   /* acc + bias + residual[M,N]             decoder_flattened.py:288-291 */
+  TNT_EPI_RESIDUAL = 3,  /* acc + bias + residual[M,N]             decoder_flattened.py:288-291 */
+  TNT_EPI_RELU_BWD = 5   /* acc * (residual[M,N] > 0): gradient through relu, residual = the saved relu output */
 } tnt_epilogue;
+
+/* operand layouts (backward passes reuse the forward weights without transposed copies):
+ *   TNT_NT  C[M,N] = A[M,K] . W[N,K]^T     forward        (W = nn.Linear weight [out, in])
+ *   TNT_NN  C[M,N] = A[M,K] . W[K,N]       data gradient  dX = dY . W
+ *   TNT_TN  C[M,N] = A[K,M]^T . W[K,N]     weight gradient dW = dY^T . X   (K = rows/tokens) */
+typedef enum { TNT_NT = 0, TNT_NN = 1, TNT_TN = 2 } tnt_gemm_layout;
 
 typedef struct {
   const void* a;  int64_t lda;        /* [M,K]  dtype_in */
@@ -69,6 +76,8 @@ typedef struct {
   int groups;
   int64_t stride_a, stride_w, stride_bias, stride_res, stride_c;
   int dtype_in, dtype_out, epilogue;
+  int layout;                         /* tnt_gemm_layout; with TNT_TN `m_dyn` bounds the reduction length K */
+  float alpha;                        /* scales the accumulator before bias / epilogue; 0 means 1 */
 } tnt_linear_params;
 int tnt_linear_fwd(const tnt_linear_params* p, tnt_stream stream);
 
@@ -308,8 +317,24 @@ int tnt_decoder_score_host(tnt_decoder* d, const int64_t* ids_host, const int64_
                            size_t staging_bytes, void* workspace, size_t workspace_bytes,
                            tnt_stream stream);
 
+/* Pipelined form of tnt_decoder_score_host with two slots: submit(slot) issues the H2D copies of that
+ * batch on a private copy stream (overlapping the compute of the other slot), then forward + loss + the
+ * D2H of (loss, n_tokens) on `stream`; wait(slot) blocks until out2_host of that slot is valid.
+ * Each slot needs its own staging buffer and out2_host; the workspace is shared. */
+int tnt_decoder_score_host_submit(tnt_decoder* d, int slot, const int64_t* ids_host, const int64_t* target_host,
+                                  const tnt_contexts* ctx_host, float* out2_host, void* staging,
+                                  size_t staging_bytes, void* workspace, size_t workspace_bytes, tnt_stream stream);
+int tnt_decoder_score_host_wait(tnt_decoder* d, int slot);
+
 /* number of kernels this library has launched since load (for bench.py's gpu_launches) */
 uint64_t tnt_launch_count(void);
+
+/* Named device-time regions, timed with CUDA events on the launching stream (off by default).
+ * Regions: "kv_proj.<source>" (the K/V projection GEMM of tnt_decoder_forward / _generate / _train).
+ * tnt_prof_read synchronises the recorded events and returns their summed duration and count. */
+void tnt_prof_enable(int on);
+void tnt_prof_reset(void);
+int tnt_prof_read(const char* name, double* ms_total, int* count);
 
 #ifdef __cplusplus
 }

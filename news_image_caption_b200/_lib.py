@@ -7,7 +7,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, 'libtnt_b200.so')
 
 TNT_F32, TNT_BF16 = 0, 1
-EPI_NONE, EPI_RELU, EPI_GLU, EPI_RESIDUAL = 0, 1, 2, 3
+EPI_NONE, EPI_RELU, EPI_GLU, EPI_RESIDUAL, EPI_RELU_BWD = 0, 1, 2, 3, 5
+LAYOUT_NT, LAYOUT_NN, LAYOUT_TN = 0, 1, 2
 MASK_NONE, MASK_KEY_PADDING, MASK_V2 = 0, 1, 2
 MAX_SOURCES, MAX_LAYERS, MAX_CLUSTERS = 4, 16, 4
 
@@ -22,7 +23,7 @@ class LinearParams(C.Structure):
     _fields_ = [('a', vp), ('lda', i64), ('w', vp), ('ldw', i64), ('bias', vp), ('residual', vp), ('ldr', i64),
                 ('c', vp), ('ldc', i64), ('M', i32), ('N', i32), ('K', i32), ('m_dyn', vp), ('groups', i32),
                 ('stride_a', i64), ('stride_w', i64), ('stride_bias', i64), ('stride_res', i64), ('stride_c', i64),
-                ('dtype_in', i32), ('dtype_out', i32), ('epilogue', i32)]
+                ('dtype_in', i32), ('dtype_out', i32), ('epilogue', i32), ('layout', i32), ('alpha', f32)]
 
 
 class DynconvParams(C.Structure):
@@ -88,6 +89,9 @@ _SIGS = {
     'tnt_last_error': (C.c_char_p, []),
     'tnt_device_check': (i32, []),
     'tnt_launch_count': (C.c_uint64, []),
+    'tnt_prof_enable': (None, [i32]),
+    'tnt_prof_reset': (None, []),
+    'tnt_prof_read': (i32, [C.c_char_p, C.POINTER(C.c_double), C.POINTER(i32)]),
     'tnt_linear_fwd': (i32, [C.POINTER(LinearParams), vp]),
     'tnt_wn_fold': (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
     'tnt_glu_interleave_bias': (i32, [vp, vp, i32, vp]),
@@ -116,6 +120,8 @@ _SIGS = {
     'tnt_decoder_generate': (i32, [vp, vp, C.POINTER(Contexts), i32, i32, vp, vp, C.POINTER(i32), vp, C.c_size_t, vp]),
     'tnt_decoder_score_host_staging_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
     'tnt_decoder_score_host': (i32, [vp, vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp, C.c_size_t, vp]),
+    'tnt_decoder_score_host_submit': (i32, [vp, i32, vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp, C.c_size_t, vp]),
+    'tnt_decoder_score_host_wait': (i32, [vp, i32]),
     'tnt_debug_force_simt_gemm': (None, [i32]),
     'tnt_debug_force_simt_attention': (None, [i32]),
 }

@@ -12,6 +12,9 @@ namespace tnt {
 // ------------------------------------------------------------------ host side: errors, launches
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
+bool prof_enabled();
+int prof_begin(const char* name, cudaStream_t st);   // -1 when profiling is off
+void prof_end(int id, cudaStream_t st);
 
 #define TNT_CHECK_ARG(cond, ...)             \
   do {                                       \

@@ -2,6 +2,9 @@
 #include <stdarg.h>
 
 #include <atomic>
+#include <mutex>
+#include <string>
+#include <vector>
 
 #include "common.cuh"
 
@@ -17,6 +20,30 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 void count_launch(int n) { g_launches.fetch_add(static_cast<uint64_t>(n), std::memory_order_relaxed); }
+
+// ---- named device-time regions (CUDA events on the launching stream), off by default.
+// bench.py uses them to time the dominant kernel INSIDE the timed step loop.
+struct ProfRec { std::string name; cudaEvent_t e0, e1; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof;
+static std::mutex g_prof_mu;
+
+bool prof_enabled() { return g_prof_on; }
+int prof_begin(const char* name, cudaStream_t st) {
+  if (!g_prof_on) return -1;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  ProfRec r;
+  r.name = name;
+  if (cudaEventCreate(&r.e0) != cudaSuccess || cudaEventCreate(&r.e1) != cudaSuccess) return -1;
+  cudaEventRecord(r.e0, st);
+  g_prof.push_back(r);
+  return static_cast<int>(g_prof.size()) - 1;
+}
+void prof_end(int id, cudaStream_t st) {
+  if (id < 0) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (id < static_cast<int>(g_prof.size())) cudaEventRecord(g_prof[id].e1, st);
+}
 
 }  // namespace tnt
 
@@ -35,5 +62,35 @@ extern "C" int tnt_device_check(void) {
     tnt::set_error("tnt_b200 is built for sm_100a only; device has compute capability %d.x", major);
     return TNT_ERR_NODEVICE;
   }
+  return TNT_OK;
+}
+
+extern "C" void tnt_prof_enable(int on) {
+  std::lock_guard<std::mutex> lk(tnt::g_prof_mu);
+  tnt::g_prof_on = on != 0;
+}
+extern "C" void tnt_prof_reset(void) {
+  std::lock_guard<std::mutex> lk(tnt::g_prof_mu);
+  for (auto& r : tnt::g_prof) {
+    cudaEventDestroy(r.e0);
+    cudaEventDestroy(r.e1);
+  }
+  tnt::g_prof.clear();
+}
+extern "C" int tnt_prof_read(const char* name, double* ms_total, int* count) {
+  std::lock_guard<std::mutex> lk(tnt::g_prof_mu);
+  double tot = 0;
+  int n = 0;
+  for (auto& r : tnt::g_prof) {
+    if (name && r.name != name) continue;
+    if (cudaEventSynchronize(r.e1) != cudaSuccess) continue;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
+      tot += ms;
+      ++n;
+    }
+  }
+  if (ms_total) *ms_total = tot;
+  if (count) *count = n;
   return TNT_OK;
 }

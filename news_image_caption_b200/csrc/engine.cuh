@@ -53,6 +53,10 @@ struct tnt_decoder {
   tnt::AdaSoftmax ada;
   void* scratch_dd = nullptr;          // [d, d] fp32 (finalize only)
   int article_idx = -1;
+  // pipelined host scoring (tnt_decoder_score_host_submit / _wait): copy stream + per-slot events
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_h2d[2] = {}, ev_free[2] = {}, ev_done[2] = {};
+  bool slot_used[2] = {false, false};
 
   int d() const { return cfg.d; }
   int nsrc() const { return cfg.n_sources; }

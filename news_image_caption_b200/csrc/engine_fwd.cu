@@ -81,8 +81,12 @@ int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStre
     TNT_LAUNCHED();
     if (ctx->S[s] == 0) continue;
     TNT_CHECK_ARG(ctx->memory[s], "decoder: context '%s' missing", c.source_names[s]);
+    char pname[40];
+    snprintf(pname, sizeof(pname), "kv_proj.%s", c.source_names[s]);
+    const int pid = prof_begin(pname, st);
     TNT_TRY(linear(ctx->memory[s], c.source_dim[s], D->wkv[s], c.source_dim[s], D->bkv[s], w.kv[s], ldkv,
                    ctx->S[s] * ctx->B, ldkv, c.source_dim[s], c.dtype, EPI_NONE, nullptr, 0, st));
+    prof_end(pid, st);
   }
   return TNT_OK;
 }

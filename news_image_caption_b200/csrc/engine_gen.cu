@@ -243,3 +243,64 @@ extern "C" int tnt_decoder_score_host(tnt_decoder* D, const int64_t* ids_host, c
   TNT_CUDA(cudaStreamSynchronize(st));
   return TNT_OK;
 }
+
+// Pipelined form: slot s's H2D copies run on a private copy stream and overlap the compute of the other
+// slot; `wait` blocks until slot s's (loss, n_tokens) have landed in out2_host.
+extern "C" int tnt_decoder_score_host_submit(tnt_decoder* D, int slot, const int64_t* ids_host,
+                                             const int64_t* target_host, const tnt_contexts* ch, float* out2_host,
+                                             void* staging, size_t staging_bytes, void* workspace,
+                                             size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && ids_host && target_host && ch && out2_host && staging && workspace, "score_host_submit: null pointer");
+  TNT_CHECK_ARG(slot == 0 || slot == 1, "score_host_submit: slot must be 0 or 1");
+  const int B = ch->B, T = ch->T;
+  Staging s = carve_staging(D, B, T, ch->S, staging);
+  if (s.total > staging_bytes) {
+    set_error("score_host_submit: staging %zu < %zu", staging_bytes, s.total);
+    return TNT_ERR_WORKSPACE;
+  }
+  if (!D->copy_stream) {
+    TNT_CUDA(cudaStreamCreateWithFlags(&D->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      TNT_CUDA(cudaEventCreateWithFlags(&D->ev_h2d[i], cudaEventDisableTiming));
+      TNT_CUDA(cudaEventCreateWithFlags(&D->ev_free[i], cudaEventDisableTiming));
+      TNT_CUDA(cudaEventCreateWithFlags(&D->ev_done[i], cudaEventDisableTiming));
+    }
+  }
+  cudaStream_t st = as_stream(stream), cs = D->copy_stream;
+  if (D->slot_used[slot]) TNT_CUDA(cudaStreamWaitEvent(cs, D->ev_free[slot], 0));   // staging of this slot consumed
+  TNT_CUDA(cudaMemcpyAsync(s.ids, ids_host, sizeof(int64_t) * B * T, cudaMemcpyHostToDevice, cs));
+  TNT_CUDA(cudaMemcpyAsync(s.tgt, target_host, sizeof(int64_t) * B * T, cudaMemcpyHostToDevice, cs));
+  tnt_contexts cd = *ch;
+  for (int i = 0; i < D->cfg.n_sources; ++i) {
+    const size_t mb = static_cast<size_t>(ch->S[i]) * B * D->cfg.source_dim[i] * D->esz();
+    if (mb) TNT_CUDA(cudaMemcpyAsync(s.mem[i], ch->memory[i], mb, cudaMemcpyHostToDevice, cs));
+    cd.memory[i] = s.mem[i];
+    if (ch->pad_mask[i] && ch->S[i]) {
+      TNT_CUDA(cudaMemcpyAsync(s.mask[i], ch->pad_mask[i], static_cast<size_t>(ch->S[i]) * B, cudaMemcpyHostToDevice, cs));
+      cd.pad_mask[i] = s.mask[i];
+    } else {
+      cd.pad_mask[i] = nullptr;
+    }
+  }
+  TNT_CUDA(cudaEventRecord(D->ev_h2d[slot], cs));
+  TNT_CUDA(cudaStreamWaitEvent(st, D->ev_h2d[slot], 0));
+  const size_t fwd = carve_fwd(D, B, T, ch->S, nullptr, true).total;
+  const size_t loss = adasoftmax_workspace_bytes(D->ada, B * T, false);
+  if (fwd + loss > workspace_bytes) {
+    set_error("score_host_submit: workspace %zu < %zu", workspace_bytes, fwd + loss);
+    return TNT_ERR_WORKSPACE;
+  }
+  TNT_TRY(tnt_decoder_forward(D, s.ids, &cd, s.X, nullptr, workspace, fwd, stream));
+  TNT_TRY(tnt_decoder_nll(D, s.X, s.tgt, B * T, s.out2, static_cast<char*>(workspace) + fwd, workspace_bytes - fwd, stream));
+  TNT_CUDA(cudaMemcpyAsync(out2_host, s.out2, 2 * sizeof(float), cudaMemcpyDeviceToHost, st));
+  TNT_CUDA(cudaEventRecord(D->ev_free[slot], st));
+  TNT_CUDA(cudaEventRecord(D->ev_done[slot], st));
+  D->slot_used[slot] = true;
+  return TNT_OK;
+}
+
+extern "C" int tnt_decoder_score_host_wait(tnt_decoder* D, int slot) {
+  TNT_CHECK_ARG(D && (slot == 0 || slot == 1) && D->slot_used[slot], "score_host_wait: slot was not submitted");
+  TNT_CUDA(cudaEventSynchronize(D->ev_done[slot]));
+  return TNT_OK;
+}

@@ -36,10 +36,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int M = g.m_dyn ? min(g.M, __ldg(g.m_dyn)) : g.M;
+  // the device-side count bounds the token dimension: output rows (NT / NN) or the reduction (TN)
+  const int dyn = g.m_dyn ? __ldg(g.m_dyn) : 0x7fffffff;
+  const int M = g.a_mn ? g.M : min(g.M, dyn);
+  const int Kred = g.a_mn ? min(g.K, dyn) : g.K;
   const int m_tiles = (M + BM - 1) / BM;
   const int total_tiles = g.groups * m_tiles * n_tiles;
-  const int num_kb = (g.K + BK - 1) / BK;
+  const int num_kb = (Kred + BK - 1) / BK;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
@@ -74,8 +77,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           ptx::mbar_wait(&empty[s], ph ^ 1);
           uint8_t* sa = smem + s * stage_bytes;
           ptx::mbar_arrive_expect_tx(&full[s], stage_bytes);
-          ptx::tma_load_3d(sa, &tmA, &full[s], kb * BK, mt * BM, ga);
-          ptx::tma_load_3d(sa + A_STAGE_BYTES, &tmW, &full[s], kb * BK, nt * BN, gw);
+          if (!g.a_mn) {
+            ptx::tma_load_3d(sa, &tmA, &full[s], kb * BK, mt * BM, ga);
+          } else {                                     // A stored [K, M]: two 64-column atoms of 64 k-rows
+            ptx::tma_load_3d(sa, &tmA, &full[s], mt * BM, kb * BK, ga);
+            ptx::tma_load_3d(sa + 8192, &tmA, &full[s], mt * BM + 64, kb * BK, ga);
+          }
+          if (!g.b_mn) {
+            ptx::tma_load_3d(sa + A_STAGE_BYTES, &tmW, &full[s], kb * BK, nt * BN, gw);
+          } else {                                     // W stored [K, N]: BN/64 atoms
+            for (int at = 0; at < BN / 64; ++at)
+              ptx::tma_load_3d(sa + A_STAGE_BYTES + at * 8192, &tmW, &full[s], nt * BN + at * 64, kb * BK, gw);
+          }
           if (++s == stages) { s = 0; ph ^= 1; }
         }
       }
@@ -84,7 +97,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (one thread)
     if (lane == 0) {
-      const uint32_t idesc = ptx::umma_idesc_bf16(BM, BN, 0, 0);
+      const uint32_t idesc = ptx::umma_idesc_bf16(BM, BN, g.a_mn, g.b_mn);
       int s = 0, it = 0;
       uint32_t ph = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
@@ -100,14 +113,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t b_addr = a_addr + A_STAGE_BYTES;
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t ad = ptx::umma_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
-            const uint64_t bd = ptx::umma_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
+            // K-major: 32 bytes per K step inside the 128-byte row; MN-major: 16 k-rows x 128 B per step,
+            // 64-element atoms 8192 B apart (LBO), 8-row groups 1024 B apart (SBO)
+            const uint64_t ad = g.a_mn ? ptx::umma_smem_desc(a_addr + k * 2048, 8192, 1024)
+                                       : ptx::umma_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
+            const uint64_t bd = g.b_mn ? ptx::umma_smem_desc(b_addr + k * 2048, 8192, 1024)
+                                       : ptx::umma_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
             ptx::umma_bf16_ss(d_tmem, ad, bd, idesc, (kb | k) != 0);
           }
           ptx::umma_commit(&empty[s]);                 // frees the smem slot when these MMAs retire
           if (++s == stages) { s = 0; ph ^= 1; }
         }
-        ptx::umma_commit(&tfull[as]);                  // accumulator complete -> epilogue
+        if (num_kb > 0) ptx::umma_commit(&tfull[as]);  // accumulator complete -> epilogue
+        else ptx::mbar_arrive(&tfull[as]);             // empty reduction: the epilogue writes zeros
       }
     }
     __syncwarp();
@@ -135,10 +153,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint32_t v[32];
         ptx::tmem_ld_32x32(taddr + c * 32, v);
         ptx::tmem_ld_wait();
+        if (EPI == EPI_SMGRAD && row >= M && row < g.M) {       // pad rows of a dynamic-M problem: zeros
+          float z[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) z[i] = 0.f;
+          epilogue_store<EPI_NONE, TOut, 32>(g, grp, row, n0, z);
+        }
         if (row < M) {
           float acc[32];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) acc[i] = __uint_as_float(v[i]);
+          for (int i = 0; i < 32; ++i) acc[i] = num_kb > 0 ? __uint_as_float(v[i]) : 0.f;
           if (EPI == EPI_LSE) {
             if (g.bias) {
 #pragma unroll
@@ -184,9 +208,11 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(GemmArgs g) {
   __shared__ float As[TK][TM + 4];
   __shared__ float Ws[TK][TN + 4];
   const int grp = blockIdx.z;
-  const int M = g.m_dyn ? min(g.M, __ldg(g.m_dyn)) : g.M;
+  const int dyn = g.m_dyn ? __ldg(g.m_dyn) : 0x7fffffff;
+  const int M = g.a_mn ? g.M : min(g.M, dyn);
+  const int Kred = g.a_mn ? min(g.K, dyn) : g.K;
   const int m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
-  if (m0 >= M) return;
+  if (m0 >= M && !(EPI == EPI_SMGRAD && m0 < g.M && m0 < ((M + 127) & ~127))) return;
   const TIn* A = reinterpret_cast<const TIn*>(g.a) + grp * g.sa;
   const TIn* W = reinterpret_cast<const TIn*>(g.w) + grp * g.sw;
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
@@ -196,13 +222,22 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(GemmArgs g) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
 
-  for (int k0 = 0; k0 < g.K; k0 += TK) {
+  for (int k0 = 0; k0 < Kred; k0 += TK) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const int idx = threadIdx.x + i * 256, r = idx >> 4, kk = idx & 15;
-      const bool kin = (k0 + kk) < g.K;
-      As[kk][r] = (kin && (m0 + r) < M) ? to_f(A[static_cast<long>(m0 + r) * g.lda + k0 + kk]) : 0.f;
-      Ws[kk][r] = (kin && (n0 + r) < g.N) ? to_f(W[static_cast<long>(n0 + r) * g.ldw + k0 + kk]) : 0.f;
+      const int idx = threadIdx.x + i * 256;
+      {
+        const int r = g.a_mn ? (idx & 63) : (idx >> 4), kk = g.a_mn ? (idx >> 6) : (idx & 15);
+        const bool in = (k0 + kk) < Kred && (m0 + r) < M;
+        const long off = g.a_mn ? static_cast<long>(k0 + kk) * g.lda + m0 + r : static_cast<long>(m0 + r) * g.lda + k0 + kk;
+        As[kk][r] = in ? to_f(A[off]) : 0.f;
+      }
+      {
+        const int r = g.b_mn ? (idx & 63) : (idx >> 4), kk = g.b_mn ? (idx >> 6) : (idx & 15);
+        const bool in = (k0 + kk) < Kred && (n0 + r) < g.N;
+        const long off = g.b_mn ? static_cast<long>(k0 + kk) * g.ldw + n0 + r : static_cast<long>(n0 + r) * g.ldw + k0 + kk;
+        Ws[kk][r] = in ? to_f(W[off]) : 0.f;
+      }
     }
     __syncthreads();
 #pragma unroll
@@ -245,6 +280,9 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(GemmArgs g) {
             make_float4(la.m, la.s, __int_as_float(la.arg), la.tz);
     } else if (row < M) {
       epilogue_store<EPI, TOut, 4>(g, grp, row, n0 + tx * 4, acc[i]);
+    } else if (EPI == EPI_SMGRAD && row < g.M) {
+      float z[4] = {0.f, 0.f, 0.f, 0.f};
+      epilogue_store<EPI_NONE, TOut, 4>(g, grp, row, n0 + tx * 4, z);
     }
   }
 }
@@ -316,17 +354,18 @@ int make_tmap_bf16_3d(CUtensorMap* tm, const void* base, long d0, long d1, long 
   return TNT_OK;
 }
 
-static int pick_bn(int M, int N, int groups) {
+static int pick_bn(int M, int N, int groups, bool b_mn = false) {
   const int m_tiles = (M + tc::BM - 1) / tc::BM;
   const int sms = num_sms();
   const int cands[4] = {256, 128, 64, 32};
-  for (int i = 0; i < 4; ++i) {
+  const int last = b_mn ? 2 : 3;                       // an MN-major W tile is built from 64-column atoms
+  for (int i = 0; i <= last; ++i) {
     const int bn = cands[i];
-    if (i < 3 && N <= cands[i + 1]) continue;          // tile would be mostly padding
+    if (i < last && N <= cands[i + 1]) continue;       // tile would be mostly padding
     const long tiles = static_cast<long>(groups) * m_tiles * ((N + bn - 1) / bn);
-    if (tiles >= sms || i == 3) return bn;
+    if (tiles >= sms || i == last) return bn;
   }
-  return 32;
+  return cands[last];
 }
 
 int gemm_tile_n(int dtype, int M, int N) { return dtype == TNT_BF16 ? pick_bn(M, N, 1) : simt::TN; }
@@ -334,8 +373,10 @@ int gemm_tile_n(int dtype, int M, int N) { return dtype == TNT_BF16 ? pick_bn(M,
 template <int EPI, typename TOut>
 static int launch_tc(const GemmArgs& g, int BN, cudaStream_t st) {
   CUtensorMap tmA, tmW;
-  TNT_TRY(make_tmap_bf16(&tmA, g.a, g.K, g.M, g.lda, g.groups, g.sa, tc::BM));
-  TNT_TRY(make_tmap_bf16(&tmW, g.w, g.K, g.N, g.ldw, g.groups, g.sw, BN));
+  if (g.a_mn) TNT_TRY(make_tmap_bf16(&tmA, g.a, g.M, g.K, g.lda, g.groups, g.sa, 64));
+  else TNT_TRY(make_tmap_bf16(&tmA, g.a, g.K, g.M, g.lda, g.groups, g.sa, tc::BM));
+  if (g.b_mn) TNT_TRY(make_tmap_bf16(&tmW, g.w, g.N, g.K, g.ldw, g.groups, g.sw, 64));
+  else TNT_TRY(make_tmap_bf16(&tmW, g.w, g.K, g.N, g.ldw, g.groups, g.sw, BN));
   const int stage_bytes = tc::A_STAGE_BYTES + BN * tc::BK * 2;
   const int stages = std::min(tc::kMaxStages, (tc::kSmemBudget - 2048) / stage_bytes);
   const int smem = stages * stage_bytes + 1024 + 512;
@@ -386,7 +427,7 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
   TNT_CHECK_ARG(epi == EPI_LSE || p->c, "linear: null output");
   TNT_CHECK_ARG(p->dtype_in == TNT_F32 || p->dtype_in == TNT_BF16, "linear: dtype_in");
   TNT_CHECK_ARG(epi != EPI_GLU || (p->N % 2 == 0), "linear: GLU needs an even N");
-  TNT_CHECK_ARG(epi != EPI_RESIDUAL || p->residual, "linear: residual epilogue without residual");
+  TNT_CHECK_ARG((epi != EPI_RESIDUAL && epi != EPI_RELU_BWD) || p->residual, "linear: residual epilogue without residual");
   if (p->M == 0) return TNT_OK;
   GemmArgs g;
   g.a = p->a; g.w = p->w; g.bias = p->bias; g.res = p->residual; g.c = p->c;
@@ -401,12 +442,19 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
   g.side = lse ? lse->side : nullptr;
   g.side_ld = lse ? lse->side_ld : 0;
   g.n_tiles = 0;
+  TNT_CHECK_ARG(p->layout >= TNT_NT && p->layout <= TNT_TN, "linear: layout");
+  g.a_mn = p->layout == TNT_TN;
+  g.b_mn = p->layout != TNT_NT;
+  g.alpha = p->alpha != 0.f ? p->alpha : 1.f;
+  g.row_lse = lse ? lse->row_lse : nullptr;
+  g.gscale = lse ? lse->gscale : 1.f;
+  TNT_CHECK_ARG(epi != EPI_SMGRAD || (lse && lse->row_lse && lse->target), "smgrad: missing row statistics");
   TNT_CHECK_ARG(epi != EPI_LSE || (lse && lse->partials && (lse->n_lse >= p->N || lse->side)), "lse: missing buffers");
   const size_t eo = dtype_size(p->dtype_out);
   const long vec = 16 / static_cast<long>(eo);
   g.vec_ok = epi == EPI_LSE ? 0
                             : (aligned16(p->c) && p->ldc % vec == 0 && g.sc % vec == 0 &&
-                               (epi != EPI_RESIDUAL ||
+                               ((epi != EPI_RESIDUAL && epi != EPI_RELU_BWD) ||
                                 (aligned16(p->residual) && p->ldr % vec == 0 && g.sres % vec == 0)));
   const bool use_tc = p->dtype_in == TNT_BF16 && !g_force_simt;
   int BN = simt::TN;
@@ -415,7 +463,7 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
                         g.sw % 8 == 0,
                     "linear(bf16): A / W must be 16-byte aligned with leading dimensions multiple of 8 (lda=%ld ldw=%ld)",
                     (long)p->lda, (long)p->ldw);
-    BN = pick_bn(g.M, g.N, g.groups);
+    BN = pick_bn(g.M, g.N, g.groups, g.b_mn != 0);
   }
   g.n_tiles = (g.N + BN - 1) / BN;
   if (n_tiles_out) *n_tiles_out = g.n_tiles;
@@ -425,6 +473,8 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
     case EPI_GLU: return dispatch_dtype<EPI_GLU>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
     case EPI_RESIDUAL: return dispatch_dtype<EPI_RESIDUAL>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
     case EPI_LSE: return dispatch_dtype<EPI_LSE>(g, p->dtype_in, TNT_F32, BN, g_force_simt, st);
+    case EPI_RELU_BWD: return dispatch_dtype<EPI_RELU_BWD>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
+    case EPI_SMGRAD: return dispatch_dtype<EPI_SMGRAD>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
   }
   set_error("linear: unknown epilogue %d", epi);
   return TNT_ERR_ARG;

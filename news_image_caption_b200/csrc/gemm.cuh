@@ -4,7 +4,7 @@
 
 namespace tnt {
 
-enum : int { EPI_NONE = 0, EPI_RELU = 1, EPI_GLU = 2, EPI_RESIDUAL = 3, EPI_LSE = 4 };
+enum : int { EPI_NONE = 0, EPI_RELU = 1, EPI_GLU = 2, EPI_RESIDUAL = 3, EPI_LSE = 4, EPI_RELU_BWD = 5, EPI_SMGRAD = 6 };
 
 struct GemmArgs {
   const void* a; const void* w; const float* bias; const void* res; void* c;
@@ -20,10 +20,17 @@ struct GemmArgs {
   int n_tiles;
   int n_lse;                // columns [0, n_lse) take part in max / sum / argmax ...
   float* side; long side_ld;  // ... columns [n_lse, N) are written raw to side[row, col - n_lse]
+  // operand layouts: a_mn = A stored [K, M] (TN), b_mn = W stored [K, N] (NN / TN)
+  int a_mn, b_mn;
+  float alpha;
+  // EPI_SMGRAD: out[m, n] = gscale * (exp(z - row_lse[m]) - (n == target[m])); rows in [M_dyn, M) get zeros
+  const float* row_lse;
+  float gscale;
 };
 
 struct LseExtra {
   const int* target; float4* partials; int n_lse; float* side; long side_ld;
+  const float* row_lse = nullptr; float gscale = 1.f;     // EPI_SMGRAD
 };
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
@@ -33,6 +40,10 @@ template <int EPI, typename TOut, int NC>
 __device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m, int n0, float (&acc)[NC]) {
   static_assert(NC % 8 == 0 || NC == 4, "NC");
   const float* bias = g.bias ? g.bias + grp * g.sbias : nullptr;
+  if (g.alpha != 1.f) {
+#pragma unroll
+    for (int i = 0; i < NC; ++i) acc[i] *= g.alpha;
+  }
   if (bias) {
 #pragma unroll
     for (int i = 0; i < NC; ++i)
@@ -59,6 +70,20 @@ __device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m
         if (c0 + i < NOUT) crow[c0 + i] = from_f<TOut>(o[i]);
     }
     return;
+  }
+  if (EPI == EPI_SMGRAD) {
+    // softmax gradient of a cluster (softmax.py:169-191 + cross_entropy backward): p - onehot(target)
+    const float lse = g.row_lse[m];
+    const int tgt = g.target[m];
+#pragma unroll
+    for (int i = 0; i < NC; ++i)
+      acc[i] = g.gscale * (__expf(acc[i] - lse) - ((n0 + i) == tgt ? 1.f : 0.f));   // lse = +inf -> ignored row
+  }
+  if (EPI == EPI_RELU_BWD) {
+    const TOut* rrow = reinterpret_cast<const TOut*>(g.res) + grp * g.sres + static_cast<long>(m) * g.ldr;
+#pragma unroll
+    for (int i = 0; i < NC; ++i)
+      if (n0 + i < g.N && !(to_f(rrow[n0 + i]) > 0.f)) acc[i] = 0.f;
   }
   if (EPI == EPI_RESIDUAL) {
     const TOut* rrow = reinterpret_cast<const TOut*>(g.res) + grp * g.sres + static_cast<long>(m) * g.ldr;

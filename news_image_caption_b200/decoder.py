@@ -316,6 +316,40 @@ class DynamicConvDecoder(nn.Module):
                    'tnt_decoder_score_host')
         return float(self._out2[0]), float(self._out2[1])
 
+    def _host_contexts(self, ids_host, contexts_host):
+        B, T = ids_host.shape
+        c = _lib.Contexts()
+        c.B, c.T = B, T
+        for i, s in enumerate(self.sources):
+            mem = contexts_host[s]
+            if mem.dtype != self.torch_dtype or not mem.is_contiguous() or mem.is_cuda:
+                raise ValueError('host context %s must be a contiguous CPU tensor of dtype %s' % (s, self.torch_dtype))
+            c.S[i] = mem.shape[0]
+            c.memory[i] = mem.data_ptr()
+            m = contexts_host.get(s + '_mask')
+            c.pad_mask[i] = m.data_ptr() if m is not None else None
+        return c
+
+    def score_host_submit(self, slot, ids_host, target_host, contexts_host):
+        """Pipelined `score_host`: enqueues batch `slot` (0 or 1) -- its H2D copies overlap the compute of
+        the other slot -- and returns immediately; `score_host_wait(slot)` returns (loss_sum, n_tokens)."""
+        L, h = _lib.lib(), self._h()
+        B, T = ids_host.shape
+        c = self._host_contexts(ids_host, contexts_host)
+        S = (C.c_int * 4)(*[c.S[i] for i in range(4)])
+        stg = self._workspace('stage%d' % slot, L.tnt_decoder_score_host_staging_bytes(h, B, T, S))
+        ws = self._workspace('score', L.tnt_decoder_workspace_bytes(h, B, T, S) +
+                             L.tnt_decoder_loss_workspace_bytes(h, B * T))
+        if getattr(self, '_out2s', None) is None:
+            self._out2s = [torch.zeros(2, dtype=torch.float32).pin_memory() for _ in range(2)]
+        _lib.check(L.tnt_decoder_score_host_submit(h, slot, _ptr(ids_host), _ptr(target_host), C.byref(c),
+                                                   _ptr(self._out2s[slot]), _ptr(stg), stg.numel(), _ptr(ws),
+                                                   ws.numel(), _stream()), 'tnt_decoder_score_host_submit')
+
+    def score_host_wait(self, slot):
+        _lib.check(_lib.lib().tnt_decoder_score_host_wait(self._h(), slot), 'tnt_decoder_score_host_wait')
+        return float(self._out2s[slot][0]), float(self._out2s[slot][1])
+
 
 class AdaptiveLoss(nn.Module):
     """criteria/adaptive_loss.py:10-91: forward(adaptive_softmax_owner, net_output, target, reduction='sum')

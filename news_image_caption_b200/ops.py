@@ -31,17 +31,25 @@ def _cuda(t):
     return t
 
 
-def linear(a, w, bias=None, epilogue=EPI_NONE, residual=None, out_dtype=None):
-    """epilogue(a[M,K] @ w[N,K]^T + bias).  For EPI_GLU `w`/`bias` rows must be pair-interleaved."""
+def linear(a, w, bias=None, epilogue=EPI_NONE, residual=None, out_dtype=None, layout=0, alpha=0.0, m_dyn=None):
+    """epilogue(a[M,K] @ w[N,K]^T + bias).  For EPI_GLU `w`/`bias` rows must be pair-interleaved.
+    layout 1 (NN): a[M,K] @ w[K,N];  layout 2 (TN): a[K,M]^T @ w[K,N] (weight gradient)."""
     a, w = _cuda(a).contiguous(), _cuda(w).contiguous()
-    M, K = a.shape
-    N = w.shape[0]
+    if layout == 0:
+        (M, K), N = a.shape, w.shape[0]
+    elif layout == 1:
+        (M, K), N = a.shape, w.shape[1]
+    else:
+        (K, M), N = a.shape, w.shape[1]
     out_dtype = out_dtype or a.dtype
     n_out = N // 2 if epilogue == EPI_GLU else N
     c = torch.empty(M, n_out, dtype=out_dtype, device=a.device)
     p = _lib.LinearParams()
-    p.a, p.lda, p.w, p.ldw = a.data_ptr(), K, w.data_ptr(), K
+    p.a, p.lda, p.w, p.ldw = a.data_ptr(), a.shape[1], w.data_ptr(), w.shape[1]
     p.bias = bias.data_ptr() if bias is not None else None
+    p.layout, p.alpha = layout, alpha
+    if m_dyn is not None:
+        p.m_dyn = m_dyn.data_ptr()
     if residual is not None:
         residual = residual.contiguous()
         p.residual, p.ldr = residual.data_ptr(), residual.shape[1]

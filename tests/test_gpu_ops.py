@@ -61,6 +61,40 @@ def test_linear_epilogues(ops, dtype):
     assert rel_err(ops.linear(a.cuda(), wi, bi, _lib.EPI_GLU), glu) < tol
 
 
+@pytest.mark.parametrize('M,N,K', [(128, 64, 64), (2048, 1024, 1024), (300, 1000, 520), (2048, 5008, 1024), (1000, 72, 4096)])
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float32])
+def test_linear_backward_layouts(ops, M, N, K, dtype):
+    """NN (dX = dY . W) and TN (dW = dY^T . X) operand layouts, used by the backward pass, incl. alpha,
+    the relu-gradient epilogue, in-place accumulation and a device-side reduction length."""
+    from news_image_caption_b200 import _lib
+    g = torch.Generator().manual_seed(M * 3 + N + K)
+    tol = 1e-5 if dtype == torch.float32 else 8e-3
+    dy = torch.randn(M, K, generator=g).to(dtype)                 # [tokens, out]
+    w = (torch.randn(K, N, generator=g) / K ** 0.5).to(dtype)     # [out, in]
+    ref = dy.double() @ w.double()
+    out = ops.linear(dy.cuda(), w.cuda(), layout=_lib.LAYOUT_NN, alpha=0.5)
+    assert rel_err(out, 0.5 * ref) < tol
+    act = torch.randn(M, N, generator=g).to(dtype)
+    out = ops.linear(dy.cuda(), w.cuda(), epilogue=_lib.EPI_RELU_BWD, residual=act.cuda(), layout=_lib.LAYOUT_NN)
+    assert rel_err(out, ref * (act.double() > 0)) < tol
+    # weight gradient: tokens = M is the reduction
+    x = torch.randn(M, N, generator=g).to(dtype)                  # [tokens, in]
+    refw = dy.double().t() @ x.double()                           # [out=K, in=N]
+    dw = ops.linear(dy.cuda(), x.cuda(), layout=_lib.LAYOUT_TN, out_dtype=torch.float32)
+    assert rel_err(dw, refw) < tol
+    acc0 = torch.randn(K, N, generator=g)
+    dw2 = ops.linear(dy.cuda(), x.cuda(), epilogue=_lib.EPI_RESIDUAL, residual=acc0.cuda(), layout=_lib.LAYOUT_TN,
+                     out_dtype=torch.float32)
+    assert rel_err(dw2, refw + acc0.double()) < tol
+    for cnt in (0, 1, 64 * (M // 128), M - 3):                    # device-side token count, rows beyond are zero
+        cnt = max(0, min(cnt, M))
+        dyz = dy.clone(); dyz[cnt:] = 0
+        c = torch.tensor([cnt], dtype=torch.int32).cuda()
+        dwc = ops.linear(dyz.cuda(), x.cuda(), layout=_lib.LAYOUT_TN, out_dtype=torch.float32, m_dyn=c)
+        refc = dy[:cnt].double().t() @ x[:cnt].double()
+        assert (dwc.cpu().double() - refc).abs().max().item() <= tol * max(1.0, refc.abs().max().item())
+
+
 def test_tc_matches_simt(ops):
     """tcgen05 GEMM against the library's own fp32-accumulating SIMT kernel on identical bf16 inputs."""
     from news_image_caption_b200 import _lib
