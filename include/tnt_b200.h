@@ -215,6 +215,18 @@ int tnt_xattn_fwd(const tnt_xattn_params* p, tnt_stream stream);
 
 
 
+/* Backward of tnt_xattn_fwd (kernel group 4): given dout (same layout as out) computes dq, dk, dv (same
+ * layouts as q, k, v).  `fwd` describes the forward call (out = its output); n_extra must be 0 (callers
+ * materialise the bias_k / zero rows as ordinary k / v rows, as the decoder engine does). */
+typedef struct {
+  tnt_xattn_params fwd;
+  const void* dout;
+  void* dq; void* dk; void* dv;
+  void* scratch; size_t scratch_bytes;   /* tnt_xattn_bwd_scratch_bytes(B, T, H, D) */
+} tnt_xattn_bwd_params;
+size_t tnt_xattn_bwd_scratch_bytes(int B, int T, int H, int D);
+int tnt_xattn_bwd(const tnt_xattn_bwd_params* p, tnt_stream stream);
+
 /* ------------------------------------------------------------------------------------------
  * AdaptiveSoftmax + AdaptiveLoss.
  *   ttl/tell/modules/softmax.py:144-222, ttl/tell/modules/criteria/adaptive_loss.py:27-73
@@ -307,6 +319,23 @@ size_t tnt_decoder_generate_workspace_bytes(const tnt_decoder* d, int B, int gen
 int tnt_decoder_generate(tnt_decoder* d, const int64_t* seed, const tnt_contexts* ctx, int gen_len, int eos,
                          int64_t* ids_out, float* logp_out, int* steps_host, void* workspace,
                          size_t workspace_bytes, tnt_stream stream);
+
+/* One training step (kernel group 4 + the forward): teacher-forced forward keeping activations,
+ * AdaptiveLoss, and the backward pass through loss, layers, K/V projections and embedding bands.
+ *   forward / loss : as tnt_decoder_forward + tnt_decoder_nll (dropout p = 0)
+ *   gradients      : d(loss_scale * sum-NLL)/d(parameter), fp32, WRITTEN into the buffer registered for each
+ *                    reference state_dict key with tnt_decoder_set_grad (same shapes as the parameters;
+ *                    weight_norm'ed linears receive weight_g / weight_v gradients, linear.py:30-33).  The tied
+ *                    output rows (softmax.py:83-86,111-132) share the embedding bands' buffers:
+ *                    adaptive_softmax.head.word_proj.weight / tail.i.2.weight have no buffer of their own.
+ *   out2           : [loss sum (nats, unscaled), number of non-pad targets]
+ * The parameter pointers given to tnt_decoder_load must still be valid (the backward reads weight_v/_g and
+ * the band tables).  Data-parallel training all-reduces the gradient buffers afterwards. */
+size_t tnt_decoder_train_workspace_bytes(const tnt_decoder* d, int B, int T, const int* S);
+int tnt_decoder_set_grad(tnt_decoder* d, const char* key, float* grad);
+int tnt_decoder_train_step(tnt_decoder* d, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,
+                           float loss_scale, float* out2, void* workspace, size_t workspace_bytes,
+                           tnt_stream stream);
 
 /* End-to-end convenience used for the e2e benchmark: ids/targets/contexts/masks in PINNED HOST
  * memory, loss read back; performs the H2D copies, forward, loss and D2H on `stream` and

@@ -66,6 +66,11 @@ class XattnParams(C.Structure):
                 ('D', i32), ('n_extra', i32), ('mask_mode', i32), ('scale', f32), ('dtype', i32), ('mask_S', i32)]
 
 
+class XattnBwdParams(C.Structure):
+    _fields_ = [('fwd', XattnParams), ('dout', vp), ('dq', vp), ('dk', vp), ('dv', vp), ('scratch', vp),
+                ('scratch_bytes', C.c_size_t)]
+
+
 class LseParams(C.Structure):
     _fields_ = [('x', vp), ('ldx', i64), ('w', vp), ('ldw', i64), ('bias', vp), ('target', vp), ('row_map', vp),
                 ('m_dyn', vp), ('stats', vp), ('workspace', vp), ('workspace_bytes', C.c_size_t), ('M', i32),
@@ -103,6 +108,8 @@ _SIGS = {
     'tnt_layernorm_bwd': (i32, [C.POINTER(LayernormBwdParams), vp]),
     'tnt_embed_fwd': (i32, [C.POINTER(EmbedParams), vp]),
     'tnt_xattn_fwd': (i32, [C.POINTER(XattnParams), vp]),
+    'tnt_xattn_bwd_scratch_bytes': (C.c_size_t, [i32, i32, i32, i32]),
+    'tnt_xattn_bwd': (i32, [C.POINTER(XattnBwdParams), vp]),
     'tnt_lse_workspace_bytes': (C.c_size_t, [i32, i32, i32]),
     'tnt_lse_fwd': (i32, [C.POINTER(LseParams), vp]),
     'tnt_decoder_create': (vp, [C.POINTER(DecoderConfig)]),
@@ -122,6 +129,9 @@ _SIGS = {
     'tnt_decoder_score_host': (i32, [vp, vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp, C.c_size_t, vp]),
     'tnt_decoder_score_host_submit': (i32, [vp, i32, vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp, C.c_size_t, vp]),
     'tnt_decoder_score_host_wait': (i32, [vp, i32]),
+    'tnt_decoder_train_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
+    'tnt_decoder_set_grad': (i32, [vp, C.c_char_p, vp]),
+    'tnt_decoder_train_step': (i32, [vp, vp, vp, C.POINTER(Contexts), f32, vp, vp, C.c_size_t, vp]),
     'tnt_debug_force_simt_gemm': (None, [i32]),
     'tnt_debug_force_simt_attention': (None, [i32]),
 }

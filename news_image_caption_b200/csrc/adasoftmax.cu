@@ -3,6 +3,7 @@
 // Reference: ttl/tell/modules/softmax.py:144-222 (adapt_target, forward, get_log_prob),
 //            ttl/tell/modules/criteria/adaptive_loss.py:27-73, final_roberta2/adaptive_loss.py:25-70.
 #include "adasoftmax.cuh"
+#include "backward.cuh"
 
 #include <algorithm>
 
@@ -349,6 +350,110 @@ int adasoftmax_logprob(const AdaSoftmax& a, const void* x, long ldx, int N, floa
   }
   logprob_norm_kernel<<<N, 256, 0, st>>>(N, a.cuts, w.head_raw, out);
   TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+
+// ---------------------------------------------------------------------------- backward (kernel group 4)
+// Gradient of gscale * AdaptiveLoss(sum) w.r.t. X and the softmax weights.  Needs the row statistics the
+// forward (adasoftmax_nll) left in its workspace.  Per cluster: dZ = gscale (softmax(z) - onehot) is produced
+// by re-running the logits GEMM with the EPI_SMGRAD epilogue (bf16 dZ, never fp32 logits), then
+// dX = dZ . W (NN) and dW = dZ^T . X (TN).  Tail rows are gathered / scattered through the forward's row lists.
+struct AdaBwdWs {
+  float* row_lse; int* row_tgt; void* dz; void* dact; void* dxc; float* dhead;
+  long ldz;
+  size_t total;
+};
+
+static AdaBwdWs carve_bwd(const AdaSoftmax& a, int N, void* ws) {
+  AdaBwdWs w;
+  const int nt = a.cuts.n - 1;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = ws ? static_cast<char*>(ws) + off : nullptr;
+    off += al256(bytes);
+    return p;
+  };
+  int max_cols = a.cuts.cut[0] + nt;
+  for (int i = 0; i < nt; ++i) max_cols = std::max(max_cols, a.cuts.cut[i + 1] - a.cuts.cut[i]);
+  w.ldz = (max_cols + 7) & ~7;
+  const size_t E = dtype_size(a.dtype);
+  w.row_lse = static_cast<float*>(take(sizeof(float) * N));
+  w.row_tgt = static_cast<int*>(take(sizeof(int) * N));
+  w.dz = take(E * N * w.ldz);
+  w.dact = take(E * N * a.d);
+  w.dxc = take(E * N * a.d);
+  w.dhead = static_cast<float*>(take(sizeof(float) * (a.cuts.cut[0] + nt) * a.d));
+  w.total = off;
+  return w;
+}
+
+// rows of `ids` per vocabulary band [edge[i], edge[i+1]) (ascending row order, as adapt_target builds them for
+// the tails): rows / loc are [n_bands, N], counts [n_bands]; head_scratch [N] receives the head targets (unused).
+int band_rows(const int64_t* ids, int N, const int* edges, int n_bands, int* head_scratch, int* rows, int* loc,
+              int* counts, cudaStream_t st) {
+  TNT_CHECK_ARG(n_bands >= 1 && n_bands + 1 <= TNT_MAX_CLUSTERS + 1 && n_bands <= TNT_MAX_CLUSTERS - 1 + 1, "band_rows: bands");
+  AdaCuts c;
+  c.n = n_bands + 1;                       // cluster 0 = ids below edges[0] (none when edges[0] == 0)
+  TNT_CHECK_ARG(c.n <= TNT_MAX_CLUSTERS, "band_rows: at most %d bands", TNT_MAX_CLUSTERS - 1);
+  for (int i = 0; i < c.n; ++i) c.cut[i] = edges[i];
+  adapt_target_kernel<<<1, 1024, 0, st>>>(ids, N, c, head_scratch, rows, loc, counts);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+size_t adasoftmax_bwd_workspace_bytes(const AdaSoftmax& a, int N) { return carve_bwd(a, N, nullptr).total; }
+
+static int gemm_call(const void* A, long lda, const void* W, long ldw, void* C, long ldc, int M, int N, int K, int dt_in,
+                     int dt_out, int layout, int epi, const int* m_dyn, const void* res, long ldr, const LseExtra* ex,
+                     cudaStream_t st) {
+  tnt_linear_params lp = {};
+  lp.a = A; lp.lda = lda; lp.w = W; lp.ldw = ldw; lp.c = C; lp.ldc = ldc; lp.residual = res; lp.ldr = ldr;
+  lp.M = M; lp.N = N; lp.K = K; lp.m_dyn = m_dyn; lp.groups = 1;
+  lp.dtype_in = dt_in; lp.dtype_out = dt_out; lp.epilogue = epi == EPI_SMGRAD ? EPI_NONE : epi; lp.layout = layout;
+  return launch_gemm(&lp, epi, ex, nullptr, st);
+}
+
+int adasoftmax_nll_bwd(const AdaSoftmax& a, const void* x, long ldx, int N, int pad, float gscale, void* ws_fwd,
+                       void* dX, long lddx, float* d_head_words, float* d_class_proj, float* const* d_proj,
+                       float* const* d_out, void* ws, size_t ws_bytes, cudaStream_t st) {
+  AdaWs f = carve(a, N, ws_fwd, false);
+  AdaBwdWs w = carve_bwd(a, N, ws);
+  if (w.total > ws_bytes) {
+    set_error("adasoftmax_nll_bwd: workspace %zu < %zu", ws_bytes, w.total);
+    return TNT_ERR_WORKSPACE;
+  }
+  const int nt = a.cuts.n - 1, d = a.d, dt = a.dtype, nh = a.cuts.cut[0] + nt;
+  const size_t E = dtype_size(dt);
+  // stale rows of the gather / projection buffers must be finite (0 x NaN inside a 64-row reduction block)
+  TNT_CUDA(cudaMemsetAsync(f.xc, 0, E * N * d, st));
+  TNT_CUDA(cudaMemsetAsync(f.proj, 0, E * N * d, st));
+  // ---- head cluster
+  TNT_TRY(smgrad_rows_head(f.head_stats, f.side, f.head_t, N, nt, a.cuts.cut[0], pad, w.row_lse, w.row_tgt, st));
+  LseExtra ex = {w.row_tgt, nullptr, 0, nullptr, 0, w.row_lse, gscale};
+  TNT_TRY(gemm_call(x, ldx, a.head_w, d, w.dz, w.ldz, N, nh, d, dt, dt, TNT_NT, EPI_SMGRAD, nullptr, nullptr, 0, &ex, st));
+  TNT_TRY(gemm_call(w.dz, w.ldz, a.head_w, d, dX, lddx, N, d, nh, dt, dt, TNT_NN, EPI_NONE, nullptr, nullptr, 0, nullptr, st));
+  TNT_TRY(gemm_call(w.dz, w.ldz, x, ldx, w.dhead, d, nh, d, N, dt, TNT_F32, TNT_TN, EPI_NONE, nullptr, nullptr, 0, nullptr, st));
+  TNT_CUDA(cudaMemcpyAsync(d_head_words, w.dhead, sizeof(float) * a.cuts.cut[0] * d, cudaMemcpyDeviceToDevice, st));
+  if (nt > 0)
+    TNT_CUDA(cudaMemcpyAsync(d_class_proj, w.dhead + static_cast<size_t>(a.cuts.cut[0]) * d, sizeof(float) * nt * d,
+                             cudaMemcpyDeviceToDevice, st));
+  // ---- tails
+  for (int i = 0; i < nt; ++i) {
+    const int* cnt = f.counts + i;
+    const int* rows = f.tail_rows + static_cast<long>(i) * N;
+    const int ncols = a.cuts.cut[i + 1] - a.cuts.cut[i];
+    TNT_TRY(gather_rows(x, ldx, rows, cnt, N, f.xc, d, d, dt, 0, 0, st));
+    TNT_TRY(tail_proj(a, i, f.xc, d, N, cnt, f.proj, st));
+    TNT_TRY(smgrad_rows_tail(f.tail_stats + static_cast<long>(i) * N, f.tail_loc + static_cast<long>(i) * N, cnt, N, pad,
+                             w.row_lse, w.row_tgt, st));
+    TNT_TRY(gemm_call(f.proj, d, a.out_w[i], d, w.dz, w.ldz, N, ncols, d, dt, dt, TNT_NT, EPI_SMGRAD, cnt, nullptr, 0, &ex, st));
+    TNT_TRY(gemm_call(w.dz, w.ldz, a.out_w[i], d, w.dact, d, N, d, ncols, dt, dt, TNT_NN, EPI_NONE, cnt, nullptr, 0, nullptr, st));
+    TNT_TRY(gemm_call(w.dz, w.ldz, f.proj, d, d_out[i], d, ncols, d, N, dt, TNT_F32, TNT_TN, EPI_NONE, cnt, nullptr, 0, nullptr, st));
+    TNT_TRY(gemm_call(w.dact, d, a.proj_w[i], d, w.dxc, d, N, d, d, dt, dt, TNT_NN, EPI_NONE, cnt, nullptr, 0, nullptr, st));
+    TNT_TRY(gemm_call(w.dact, d, f.xc, d, d_proj[i], d, d, d, N, dt, TNT_F32, TNT_TN, EPI_NONE, cnt, nullptr, 0, nullptr, st));
+    TNT_TRY(scatter_add_rows(w.dxc, d, rows, cnt, N, dX, lddx, d, dt, 0, 0, st));
+  }
   return TNT_OK;
 }
 

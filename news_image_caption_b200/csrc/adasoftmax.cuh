@@ -25,6 +25,15 @@ int lse_gemm(const void* x, long ldx, const void* w, long ldw, const float* bias
 size_t adasoftmax_workspace_bytes(const AdaSoftmax& a, int N, bool logprob);
 int adasoftmax_nll(const AdaSoftmax& a, const void* x, long ldx, const int64_t* target, int N, int pad, float* out2,
                    void* ws, size_t ws_bytes, cudaStream_t st);
+// gradient of gscale * sum-NLL; `ws_fwd` is the workspace adasoftmax_nll ran in (row statistics are read back).
+// dX [N, d] engine dtype (written), d_head_words [cut0, d], d_class_proj [n_tails, d], d_proj[i] [d, d],
+// d_out[i] [n_i, d]: fp32, written.
+size_t adasoftmax_bwd_workspace_bytes(const AdaSoftmax& a, int N);
+int adasoftmax_nll_bwd(const AdaSoftmax& a, const void* x, long ldx, int N, int pad, float gscale, void* ws_fwd,
+                       void* dX, long lddx, float* d_head_words, float* d_class_proj, float* const* d_proj,
+                       float* const* d_out, void* ws, size_t ws_bytes, cudaStream_t st);
+int band_rows(const int64_t* ids, int N, const int* edges, int n_bands, int* head_scratch, int* rows, int* loc,
+              int* counts, cudaStream_t st);
 int adasoftmax_greedy(const AdaSoftmax& a, const void* x, long ldx, int N, int64_t* tok, float* logp, void* ws,
                       size_t ws_bytes, cudaStream_t st);
 int adasoftmax_logprob(const AdaSoftmax& a, const void* x, long ldx, int N, float* out, void* ws, size_t ws_bytes,

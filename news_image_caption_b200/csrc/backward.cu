@@ -1,0 +1,397 @@
+// Backward-pass helper kernels (HBM-bound glue of kernel group 4): GLU gradient, bias (column) sums,
+// weight-norm gradient, row permutations / gathers / scatters, embedding-table scatter, bias_k/bias_v rows.
+// Reference ops they differentiate: decoder_flattened.py:281-345 (layer), linear.py:7-33 (weight_norm),
+// adaptive.py:61-76 (embedding bands), softmax.py:144-191 (adaptive softmax).
+#include "backward.cuh"
+
+namespace tnt {
+namespace {
+
+// ------------------------------------------------------------------------------ GLU backward
+template <typename T>
+__global__ void __launch_bounds__(256) glu_bwd_kernel(const T* raw, long ldraw, const T* dh, long lddh, T* draw,
+                                                      long lddraw, int N, int C) {
+  const int nv = C >> 3;                       // 8 outputs <-> 16 interleaved pre-activations
+  const long total = static_cast<long>(N) * nv;
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += gridDim.x * 256L) {
+    const int r = static_cast<int>(i / nv), vc = static_cast<int>(i - static_cast<long>(r) * nv);
+    float g[8], p0[8], p1[8], o0[8], o1[8];
+    load8(dh + r * lddh + vc * 8, g);
+    load8(raw + r * ldraw + vc * 16, p0);
+    load8(raw + r * ldraw + vc * 16 + 8, p1);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float a = j < 4 ? p0[2 * j] : p1[2 * (j - 4)];
+      const float b = j < 4 ? p0[2 * j + 1] : p1[2 * (j - 4) + 1];
+      const float s = sigmoidf_(b);
+      const float da = g[j] * s, db = g[j] * a * s * (1.f - s);
+      if (j < 4) { o0[2 * j] = da; o0[2 * j + 1] = db; }
+      else { o1[2 * (j - 4)] = da; o1[2 * (j - 4) + 1] = db; }
+    }
+    store8(draw + r * lddraw + vc * 16, o0);
+    store8(draw + r * lddraw + vc * 16 + 8, o1);
+  }
+}
+
+// ------------------------------------------------------------------------------ column sums
+// block = 32 x 8: threadIdx.x owns 8 consecutive columns, threadIdx.y strides the rows of this block's chunk
+constexpr int kCsRows = 256;
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_kernel(const T* x, long ldx, int M, int N, const int* m_dyn, float* out,
+                                                     int deinterleave, int vec) {
+  __shared__ float red[8][32][8];
+  const int Me = m_dyn ? min(M, *m_dyn) : M;
+  const int c0 = (blockIdx.x * 32 + threadIdx.x) * 8;
+  const int r0 = blockIdx.y * kCsRows;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (c0 < N) {
+    const int rend = min(Me, r0 + kCsRows);
+    for (int r = r0 + threadIdx.y; r < rend; r += 8) {
+      if (vec && c0 + 8 <= N) {
+        float v[8];
+        load8(x + static_cast<long>(r) * ldx + c0, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += v[j];
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (c0 + j < N) acc[j] += to_f(x[static_cast<long>(r) * ldx + c0 + j]);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.y][threadIdx.x][j] = acc[j];
+  __syncthreads();
+  if (threadIdx.y == 0 && c0 < N) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int y = 0; y < 8; ++y) s += red[y][threadIdx.x][j];
+      const int c = c0 + j;
+      if (c < N) {
+        const int o = deinterleave ? ((c & 1) ? (N >> 1) + (c >> 1) : (c >> 1)) : c;
+        atomicAdd(out + o, s);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------ weight-norm backward
+// one warp per parameter row
+__global__ void __launch_bounds__(256) wn_bwd_kernel(const float* v, const float* g, const float* dW, long lddw,
+                                                     float* dv, float* dg, int rows, int cols, int glu) {
+  const int lane = threadIdx.x & 31;
+  const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int rw = glu ? (r < (rows >> 1) ? 2 * r : 2 * (r - (rows >> 1)) + 1) : r;
+  const float* vr = v + static_cast<long>(r) * cols;
+  const float* dr = dW + static_cast<long>(rw) * lddw;
+  float* o = dv + static_cast<long>(r) * cols;
+  if (!g) {
+    for (int c = lane; c < cols; c += 32) o[c] = dr[c];
+    return;
+  }
+  float nn = 0.f, dot = 0.f;
+  for (int c = lane; c < cols; c += 32) {
+    const float a = vr[c];
+    nn = fmaf(a, a, nn);
+    dot = fmaf(a, dr[c], dot);
+  }
+  nn = warp_sum(nn);
+  dot = warp_sum(dot);
+  const float n = sqrtf(nn), gg = g[r];
+  const float k1 = gg / n, k2 = dot / nn;
+  for (int c = lane; c < cols; c += 32) o[c] = k1 * (dr[c] - k2 * vr[c]);
+  if (lane == 0) dg[r] = dot / n;
+}
+
+// ------------------------------------------------------------------------------ row movers (warp per row)
+__device__ __forceinline__ int remap_row(int r, int mB, int mT) {   // b*T + t -> t*B + b
+  return mB > 0 ? (r % mT) * mB + r / mT : r;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) permute_rows_kernel(const T* src, T* dst, int B, int Tn, int C, int to_tb) {
+  const int lane = threadIdx.x & 31;
+  const int rows = B * Tn;
+  for (int r = blockIdx.x * 8 + (threadIdx.x >> 5); r < rows; r += gridDim.x * 8) {
+    // r indexes the b*T + t order
+    const int tb = (r % Tn) * B + r / Tn;
+    const T* s = src + static_cast<long>(to_tb ? r : tb) * C;
+    T* d = dst + static_cast<long>(to_tb ? tb : r) * C;
+    for (int vc = lane; vc < (C >> 3); vc += 32) {
+      float v[8];
+      load8(s + vc * 8, v);
+      store8(d + vc * 8, v);
+    }
+  }
+}
+
+// mode 0: out[j] = src[map(rows[j])];  mode 1: dst[map(rows[j])] += src[j]
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) move_rows_kernel(const T* src, long lds, const int* rows, const int* count,
+                                                        T* dst, long ldd, int C, int mB, int mT) {
+  const int lane = threadIdx.x & 31;
+  const int n = *count;
+  for (int j = blockIdx.x * 8 + (threadIdx.x >> 5); j < n; j += gridDim.x * 8) {
+    const int rr = remap_row(rows[j], mB, mT);
+    const T* s = src + static_cast<long>(MODE == 0 ? rr : j) * lds;
+    T* d = dst + static_cast<long>(MODE == 0 ? j : rr) * ldd;
+    for (int vc = lane; vc < (C >> 3); vc += 32) {
+      float v[8];
+      load8(s + vc * 8, v);
+      if (MODE == 1) {
+        float o[8];
+        load8(d + vc * 8, o);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] += o[i];
+      }
+      store8(d + vc * 8, v);
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) gather_table_kernel(const float* table, long ldt, const int* loc, const int* count,
+                                                           T* out, long ldo, int C) {
+  const int lane = threadIdx.x & 31;
+  const int n = *count;
+  for (int j = blockIdx.x * 8 + (threadIdx.x >> 5); j < n; j += gridDim.x * 8) {
+    const float* s = table + static_cast<long>(loc[j]) * ldt;
+    T* d = out + static_cast<long>(j) * ldo;
+    for (int vc = lane; vc < (C >> 3); vc += 32) {
+      float v[8];
+      load8(s + vc * 8, v);
+      store8(d + vc * 8, v);
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) scatter_table_kernel(const T* src, long lds, const int* loc, const int* count,
+                                                            float* grad, long ldg, int C) {
+  const int lane = threadIdx.x & 31;
+  const int n = *count;
+  for (int j = blockIdx.x * 8 + (threadIdx.x >> 5); j < n; j += gridDim.x * 8) {
+    const int l = loc[j];
+    if (l == 0) continue;                                 // nn.Embedding(padding_idx=0): no gradient
+    const T* s = src + static_cast<long>(j) * lds;
+    float* d = grad + static_cast<long>(l) * ldg;
+    for (int vc = lane; vc < (C >> 3); vc += 32) {
+      float v[8];
+      load8(s + vc * 8, v);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) atomicAdd(d + vc * 8 + i, v[i]);
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) kv_extra_grad_kernel(const T* dkv, long ld, int S, int B, int ncols, float* out) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= ncols) return;
+  float s = 0.f;
+  for (int b = 0; b < B; ++b) s += to_f(dkv[(static_cast<long>(S) * B + b) * ld + c]);
+  out[c] = s;
+}
+
+// dst[r, :] += sum_{s in [s0, ns)} src[r, s*C : (s+1)*C]
+template <typename T>
+__global__ void __launch_bounds__(256) add_col_blocks_kernel(T* dst, long ldd, const T* src, long lds, int N, int C,
+                                                             int s0, int ns) {
+  const int nv = C >> 3;
+  const long total = static_cast<long>(N) * nv;
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < total; i += gridDim.x * 256L) {
+    const int r = static_cast<int>(i / nv), vc = static_cast<int>(i - static_cast<long>(r) * nv);
+    float a[8];
+    load8(dst + r * ldd + vc * 8, a);
+    for (int s = s0; s < ns; ++s) {
+      float v[8];
+      load8(src + r * lds + static_cast<long>(s) * C + vc * 8, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a[j] += v[j];
+    }
+    store8(dst + r * ldd + vc * 8, a);
+  }
+}
+
+__global__ void __launch_bounds__(256) smgrad_rows_head_kernel(const float4* hs, const float* side, const int* head_t,
+                                                               int N, int nt, int cut0, int pad, float* row_lse,
+                                                               int* row_tgt) {
+  const int r = blockIdx.x * 256 + threadIdx.x;
+  if (r >= N) return;
+  const int ht = head_t[r];
+  if (ht == pad) {                                        // ignore_index inside the head cluster
+    row_lse[r] = INFINITY;
+    row_tgt[r] = -1;
+    return;
+  }
+  const float4 st = hs[r];
+  float M = st.x;
+  for (int i = 0; i < nt; ++i) M = fmaxf(M, side[static_cast<long>(r) * nt + i]);
+  float s = st.y * __expf(st.x - M);
+  for (int i = 0; i < nt; ++i) s += __expf(side[static_cast<long>(r) * nt + i] - M);
+  row_lse[r] = M + __logf(s);
+  row_tgt[r] = ht;
+}
+
+__global__ void __launch_bounds__(256) smgrad_rows_tail_kernel(const float4* ts, const int* tail_loc, const int* count,
+                                                               int N, int pad, float* row_lse, int* row_tgt) {
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j >= N) return;
+  if (j >= *count || tail_loc[j] == pad) {                // beyond the tail's rows, or ignore_index (local id 1)
+    row_lse[j] = INFINITY;
+    row_tgt[j] = -1;
+    return;
+  }
+  const float4 st = ts[j];
+  row_lse[j] = st.x + __logf(st.y);
+  row_tgt[j] = tail_loc[j];
+}
+
+inline int grid_for(long work, int per_block) {
+  return static_cast<int>(std::min<long>((work + per_block - 1) / per_block, 8L * num_sms()));
+}
+}  // namespace
+
+int glu_bwd(const void* raw, long ldraw, const void* dh, long lddh, void* draw, long lddraw, int N, int C, int dtype,
+            cudaStream_t st) {
+  TNT_CHECK_ARG(raw && dh && draw && C % 8 == 0, "glu_bwd: bad arguments");
+  TNT_CHECK_ALIGN(aligned16(raw) && aligned16(dh) && aligned16(draw) && ldraw % 8 == 0 && lddh % 8 == 0 && lddraw % 8 == 0,
+                  "glu_bwd: alignment");
+  if (N == 0) return TNT_OK;
+  const int grid = grid_for(static_cast<long>(N) * (C >> 3), 256);
+  if (dtype == TNT_BF16)
+    glu_bwd_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<const bf16*>(raw), ldraw, static_cast<const bf16*>(dh), lddh,
+                                               static_cast<bf16*>(draw), lddraw, N, C);
+  else
+    glu_bwd_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(raw), ldraw, static_cast<const float*>(dh),
+                                                lddh, static_cast<float*>(draw), lddraw, N, C);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int colsum(const void* x, long ldx, int M, int N, const int* m_dyn, float* out, int dtype, bool deinterleave,
+           bool accumulate, cudaStream_t st) {
+  TNT_CHECK_ARG(x && out && N > 0, "colsum: bad arguments");
+  if (!accumulate) TNT_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * N, st));
+  if (M == 0) return TNT_OK;
+  const int vec = aligned16(x) && ldx % 8 == 0;
+  dim3 grid((N + 255) / 256, (M + kCsRows - 1) / kCsRows), block(32, 8);
+  if (dtype == TNT_BF16)
+    colsum_kernel<bf16><<<grid, block, 0, st>>>(static_cast<const bf16*>(x), ldx, M, N, m_dyn, out, deinterleave, vec);
+  else
+    colsum_kernel<float><<<grid, block, 0, st>>>(static_cast<const float*>(x), ldx, M, N, m_dyn, out, deinterleave, vec);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int wn_bwd(const float* v, const float* g, const float* dW, long lddw, float* dv, float* dg, int rows, int cols,
+           bool glu_interleave, cudaStream_t st) {
+  TNT_CHECK_ARG(v && dW && dv && (!g || dg), "wn_bwd: bad arguments");
+  wn_bwd_kernel<<<(rows + 7) / 8, 256, 0, st>>>(v, g, dW, lddw, dv, dg, rows, cols, glu_interleave ? 1 : 0);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+
+int permute_rows(const void* src, void* dst, int B, int T, int C, int dtype, bool to_tb, cudaStream_t st) {
+  TNT_CHECK_ARG(src && dst && C % 8 == 0, "permute_rows: bad arguments");
+  if (B * T == 0) return TNT_OK;
+  const int grid = grid_for(static_cast<long>(B) * T, 8);
+  if (dtype == TNT_BF16)
+    permute_rows_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<const bf16*>(src), static_cast<bf16*>(dst), B, T, C, to_tb);
+  else
+    permute_rows_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(src), static_cast<float*>(dst), B, T, C, to_tb);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int scatter_add_rows(const void* src, long lds, const int* rows, const int* count, int max_rows, void* dst, long ldd,
+                     int C, int dtype, int map_B, int map_T, cudaStream_t st) {
+  if (max_rows == 0) return TNT_OK;
+  const int grid = grid_for(max_rows, 8);
+  if (dtype == TNT_BF16)
+    move_rows_kernel<bf16, 1><<<grid, 256, 0, st>>>(static_cast<const bf16*>(src), lds, rows, count, static_cast<bf16*>(dst), ldd, C, map_B, map_T);
+  else
+    move_rows_kernel<float, 1><<<grid, 256, 0, st>>>(static_cast<const float*>(src), lds, rows, count, static_cast<float*>(dst), ldd, C, map_B, map_T);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int gather_rows(const void* src, long lds, const int* rows, const int* count, int max_rows, void* out, long ldo, int C,
+                int dtype, int map_B, int map_T, cudaStream_t st) {
+  if (max_rows == 0) return TNT_OK;
+  const int grid = grid_for(max_rows, 8);
+  if (dtype == TNT_BF16)
+    move_rows_kernel<bf16, 0><<<grid, 256, 0, st>>>(static_cast<const bf16*>(src), lds, rows, count, static_cast<bf16*>(out), ldo, C, map_B, map_T);
+  else
+    move_rows_kernel<float, 0><<<grid, 256, 0, st>>>(static_cast<const float*>(src), lds, rows, count, static_cast<float*>(out), ldo, C, map_B, map_T);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int gather_table_rows(const float* table, long ldt, const int* loc, const int* count, int max_rows, void* out, long ldo,
+                      int C, int dtype, cudaStream_t st) {
+  if (max_rows == 0) return TNT_OK;
+  const int grid = grid_for(max_rows, 8);
+  if (dtype == TNT_BF16)
+    gather_table_kernel<bf16><<<grid, 256, 0, st>>>(table, ldt, loc, count, static_cast<bf16*>(out), ldo, C);
+  else
+    gather_table_kernel<float><<<grid, 256, 0, st>>>(table, ldt, loc, count, static_cast<float*>(out), ldo, C);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int scatter_table_grad(const void* src, long lds, const int* loc, const int* count, int max_rows, float* grad, long ldg,
+                       int C, int dtype, cudaStream_t st) {
+  if (max_rows == 0) return TNT_OK;
+  const int grid = grid_for(max_rows, 8);
+  if (dtype == TNT_BF16)
+    scatter_table_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<const bf16*>(src), lds, loc, count, grad, ldg, C);
+  else
+    scatter_table_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(src), lds, loc, count, grad, ldg, C);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int kv_extra_grad(const void* dkv, long ld, int S, int B, int ncols, float* out, int dtype, cudaStream_t st) {
+  const int grid = (ncols + 255) / 256;
+  if (dtype == TNT_BF16)
+    kv_extra_grad_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<const bf16*>(dkv), ld, S, B, ncols, out);
+  else
+    kv_extra_grad_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(dkv), ld, S, B, ncols, out);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int smgrad_rows_head(const float4* head_stats, const float* side, const int* head_t, int N, int n_tails, int cut0,
+                     int pad, float* row_lse, int* row_tgt, cudaStream_t st) {
+  if (N == 0) return TNT_OK;
+  smgrad_rows_head_kernel<<<(N + 255) / 256, 256, 0, st>>>(head_stats, side, head_t, N, n_tails, cut0, pad, row_lse, row_tgt);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int smgrad_rows_tail(const float4* tail_stats, const int* tail_loc, const int* count, int N, int pad, float* row_lse,
+                     int* row_tgt, cudaStream_t st) {
+  if (N == 0) return TNT_OK;
+  smgrad_rows_tail_kernel<<<(N + 255) / 256, 256, 0, st>>>(tail_stats, tail_loc, count, N, pad, row_lse, row_tgt);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int add_col_blocks(void* dst, long ldd, const void* src, long lds, int N, int C, int s0, int ns, int dtype,
+                   cudaStream_t st) {
+  if (N == 0 || s0 >= ns) return TNT_OK;
+  const int grid = grid_for(static_cast<long>(N) * (C >> 3), 256);
+  if (dtype == TNT_BF16)
+    add_col_blocks_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<bf16*>(dst), ldd, static_cast<const bf16*>(src), lds, N, C, s0, ns);
+  else
+    add_col_blocks_kernel<float><<<grid, 256, 0, st>>>(static_cast<float*>(dst), ldd, static_cast<const float*>(src), lds, N, C, s0, ns);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+}  // namespace tnt

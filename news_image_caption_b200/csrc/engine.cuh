@@ -52,6 +52,9 @@ struct tnt_decoder {
   float* pos_table = nullptr;          // [max_positions, d]
   tnt::AdaSoftmax ada;
   void* scratch_dd = nullptr;          // [d, d] fp32 (finalize only)
+  void* emb_proj[TNT_MAX_CLUSTERS] = {};   // band projections [d, dim_i] in the engine dtype (training backward)
+  int emb_dim[TNT_MAX_CLUSTERS] = {};
+  std::map<std::string, float*> grads; // training: fp32 gradient buffer per state_dict key (tnt_decoder_set_grad)
   int article_idx = -1;
   // pipelined host scoring (tnt_decoder_score_host_submit / _wait): copy stream + per-slot events
   cudaStream_t copy_stream = nullptr;
@@ -74,11 +77,13 @@ namespace tnt {
 // forward workspace (teacher forcing and single-step share it; N = T*B rows)
 struct FwdWs {
   void *X0, *X1, *h, *logits, *cbuf, *ybuf, *Q, *AO, *CAT, *F;
+  void *ybuf2, *CATln;     // inference: aliases of ybuf / CAT; training keeps the pre-LayerNorm tensors
   void* kv[TNT_MAX_SOURCES];
   size_t total;
 };
 FwdWs carve_fwd(const tnt_decoder* d, int B, int T, const int* S, void* ws, bool with_kv);
 
+int embed(tnt_decoder* d, const int64_t* ids, int B, int T, void* out, const int* start_pos, cudaStream_t st);
 int project_kv(tnt_decoder* d, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st);
 // one decoder layer on N = T*B rows; `ring`/`pos` != NULL selects the single-step conv (T must be 1)
 int run_layer(tnt_decoder* d, int l, const tnt_contexts* ctx, const FwdWs& w, const void* Xin, void* Xout, int B, int T,

@@ -60,6 +60,8 @@ FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool
   w.cbuf = take(N * d * E); w.ybuf = take(N * d * E);
   w.Q = take(N * ns * d * E); w.AO = take(N * ns * d * E); w.CAT = take(N * ns * d * E);
   w.F = take(N * c.ffn * E);
+  w.ybuf2 = w.ybuf;
+  w.CATln = w.CAT;
   for (size_t s = 0; s < ns; ++s)
     w.kv[s] = with_kv ? take(static_cast<size_t>(S[s] + 2) * B * c.n_layers * 2 * d * E) : nullptr;
   w.total = off;
@@ -142,17 +144,17 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
   }
   TNT_TRY(linear(w.AO, static_cast<long>(ns) * d, L.wo, d, L.bo, w.CAT, static_cast<long>(ns) * d, N, d, d, dt, EPI_RESIDUAL,
                  w.X1, d, st, ns, d, static_cast<long>(d) * d, d, 0, d));
-  TNT_TRY(layernorm(w.CAT, w.CAT, d, L.ln_src_g, L.ln_src_b, N * ns, d, ns, dt, 0, 0, st));
-  TNT_TRY(linear(w.CAT, static_cast<long>(ns) * d, L.wc, static_cast<long>(ns) * d, L.bc, w.X0, d, N, d, ns * d, dt, EPI_NONE,
+  TNT_TRY(layernorm(w.CAT, w.CATln, d, L.ln_src_g, L.ln_src_b, N * ns, d, ns, dt, 0, 0, st));
+  TNT_TRY(linear(w.CATln, static_cast<long>(ns) * d, L.wc, static_cast<long>(ns) * d, L.bc, w.X0, d, N, d, ns * d, dt, EPI_NONE,
                  nullptr, 0, st));
   // feed-forward
   TNT_TRY(linear(w.X0, d, L.wf1, d, L.bf1, w.F, c.ffn, N, c.ffn, d, dt, EPI_RELU, nullptr, 0, st));
-  TNT_TRY(linear(w.F, c.ffn, L.wf2, c.ffn, L.bf2, w.ybuf, d, N, d, c.ffn, dt, EPI_RESIDUAL, w.X0, d, st));
-  TNT_TRY(layernorm(w.ybuf, Xout, d, L.ln_f_g, L.ln_f_b, N, d, 1, dt, transpose_out ? T : 0, transpose_out ? B : 0, st));
+  TNT_TRY(linear(w.F, c.ffn, L.wf2, c.ffn, L.bf2, w.ybuf2, d, N, d, c.ffn, dt, EPI_RESIDUAL, w.X0, d, st));
+  TNT_TRY(layernorm(w.ybuf2, Xout, d, L.ln_f_g, L.ln_f_b, N, d, 1, dt, transpose_out ? T : 0, transpose_out ? B : 0, st));
   return TNT_OK;
 }
 
-static int embed(tnt_decoder* D, const int64_t* ids, int B, int T, void* out, const int* start_pos, cudaStream_t st) {
+int embed(tnt_decoder* D, const int64_t* ids, int B, int T, void* out, const int* start_pos, cudaStream_t st) {
   tnt_embed_params e = {};
   e.ids = ids; e.table = D->table; e.pos_table = D->pos_table; e.out = out; e.ldo = D->cfg.d; e.start_pos = start_pos;
   e.B = B; e.T = T; e.d = D->cfg.d; e.n_pos = D->cfg.max_positions; e.pad_idx = D->cfg.pad_idx; e.dtype = D->cfg.dtype;

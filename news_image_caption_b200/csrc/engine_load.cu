@@ -70,6 +70,7 @@ size_t plan(tnt_decoder* D, char* base) {
     D->ada.out_w[i] = a.take(static_cast<size_t>(c.cutoffs[i + 1] - c.cutoffs[i]) * d * E);
   }
   D->scratch_dd = a.take(d * d * 4);
+  for (int i = 0; i < c.n_clusters; ++i) D->emb_proj[i] = a.take(d * d * E);
   return a.off;
 }
 
@@ -263,6 +264,8 @@ extern "C" int tnt_decoder_finalize(tnt_decoder* D, tnt_stream stream) {
           set_error("decoder_finalize: embedding band %d has an unexpected shape", i);
           return TNT_ERR_ARG;
         }
+        D->emb_dim[i] = dim_i;
+        L.matrix(prj->data, D->emb_proj[i], d, dim_i);
         scale_kernel<<<64, 256, 0, L.st>>>(prj->data, static_cast<float*>(D->scratch_dd), static_cast<long>(d) * dim_i,
                                            sqrtf(static_cast<float>(d)));
         count_launch();
@@ -306,7 +309,7 @@ extern "C" int tnt_decoder_finalize(tnt_decoder* D, tnt_stream stream) {
   }
   if (L.err != TNT_OK) return L.err;
   TNT_CUDA(cudaGetLastError());
-  D->raw.clear();
+  // the raw (fp32 master) pointers are kept: the training backward reads weight_v / weight_g / the band tables
   D->finalized = true;
   return TNT_OK;
 }

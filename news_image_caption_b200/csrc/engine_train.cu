@@ -1,0 +1,433 @@
+// Decoder engine: one training step = teacher-forced forward (activations kept) + AdaptiveLoss + backward
+// through the loss, every decoder layer, the K/V projections and the embedding -- gradients land in the
+// caller's fp32 buffers, one per reference state_dict key (tnt_decoder_set_grad).
+// What is differentiated (dropout p = 0, the parity configuration):
+//   DynamicConvDecoderLayer.forward  ttl/tell/models/decoder_flattened.py:271-345, decoder_faces_objects.py:283-393
+//   MultiHeadAttention               ttl/tell/modules/attention/multi_head.py:288-486
+//   GehringLinear weight_norm        ttl/tell/modules/linear.py:7-33
+//   AdaptiveSoftmax / AdaptiveLoss   ttl/tell/modules/softmax.py:144-191, criteria/adaptive_loss.py:27-73
+//   AdaptiveEmbedding                ttl/tell/modules/token_embedders/adaptive.py:61-76
+// The exchange step of data-parallel training (gradient all-reduce) happens outside, over the flat gradient
+// arena these buffers live in.
+#include "backward.cuh"
+#include "engine.cuh"
+
+namespace tnt {
+
+int xattn_check(const tnt_xattn_params* p);
+
+namespace {
+inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
+
+struct LayerAct {
+  void *h, *logits, *cbuf, *yc, *X1, *Q, *AO, *CATpre, *CATln, *X0, *F, *yf, *Xout;
+};
+
+struct TrainWs {
+  void* emb;                                   // layer-0 input [N, d]
+  LayerAct act[TNT_MAX_LAYERS];
+  void* kv[TNT_MAX_SOURCES];
+  void* dkv[TNT_MAX_SOURCES];
+  void *Xbt, *dXbt;                            // decoder output / its gradient in B x T row order
+  void *gA, *gB, *gC, *gD;                     // [N, d] gradient ping-pong buffers
+  void *dQ, *dAO, *dCAT, *dCATp;               // [N, ns*d]
+  void *dF;                                    // [N, ffn]
+  void *raw, *draw;                            // [N, 2d]
+  void *dlogits;                               // [N, ldl]
+  float* dW;                                   // fp32 scratch for weight-normed matrices / K-V / embedding grads
+  float* attn_scr;                             // [B, H, T, D] fp32
+  float* vecs;                                 // [L*2d] fp32 scratch (K/V bias rows)
+  int *band_rows, *band_loc, *band_cnt, *band_head;
+  void *G, *Hrows, *dH;                        // embedding backward [N, d]
+  void* loss_fwd; size_t loss_fwd_bytes;
+  void* loss_bwd; size_t loss_bwd_bytes;
+  size_t total;
+};
+
+TrainWs carve_train(const tnt_decoder* D, int B, int T, const int* S, void* ws) {
+  const tnt_decoder_config& c = D->cfg;
+  const size_t E = D->esz(), N = static_cast<size_t>(B) * T, d = c.d, ns = c.n_sources, L = c.n_layers;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    void* p = ws ? static_cast<char*>(ws) + off : nullptr;
+    off += al256(bytes);
+    return p;
+  };
+  TrainWs w;
+  w.emb = take(N * d * E);
+  for (size_t l = 0; l < L; ++l) {
+    LayerAct& a = w.act[l];
+    a.h = take(N * d * E); a.logits = take(N * D->ld_logits(c.kernels[l]) * E); a.cbuf = take(N * d * E);
+    a.yc = take(N * d * E); a.X1 = take(N * d * E); a.Q = take(N * ns * d * E); a.AO = take(N * ns * d * E);
+    a.CATpre = take(N * ns * d * E); a.CATln = take(N * ns * d * E); a.X0 = take(N * d * E);
+    a.F = take(N * c.ffn * E); a.yf = take(N * d * E); a.Xout = take(N * d * E);
+  }
+  size_t max_kdim = d;
+  for (size_t s = 0; s < ns; ++s) {
+    const size_t bytes = static_cast<size_t>(S[s] + 2) * B * L * 2 * d * E;
+    w.kv[s] = take(bytes);
+    w.dkv[s] = take(bytes);
+    max_kdim = std::max<size_t>(max_kdim, c.source_dim[s]);
+  }
+  w.Xbt = take(N * d * E); w.dXbt = take(N * d * E);
+  w.gA = take(N * d * E); w.gB = take(N * d * E); w.gC = take(N * d * E); w.gD = take(N * d * E);
+  w.dQ = take(N * ns * d * E); w.dAO = take(N * ns * d * E); w.dCAT = take(N * ns * d * E); w.dCATp = take(N * ns * d * E);
+  w.dF = take(N * c.ffn * E);
+  w.raw = take(N * 2 * d * E); w.draw = take(N * 2 * d * E);
+  w.dlogits = take(N * D->max_ld_logits() * E);
+  size_t dw = std::max<size_t>(2 * d * d, static_cast<size_t>(c.ffn) * d);
+  dw = std::max(dw, d * ns * d);
+  dw = std::max(dw, L * 2 * d * max_kdim);
+  w.dW = static_cast<float*>(take(dw * sizeof(float)));
+  w.attn_scr = static_cast<float*>(take(N * d * sizeof(float)));
+  w.vecs = static_cast<float*>(take(L * 2 * d * sizeof(float)));
+  w.band_rows = static_cast<int*>(take(sizeof(int) * N * TNT_MAX_CLUSTERS));
+  w.band_loc = static_cast<int*>(take(sizeof(int) * N * TNT_MAX_CLUSTERS));
+  w.band_cnt = static_cast<int*>(take(sizeof(int) * TNT_MAX_CLUSTERS));
+  w.band_head = static_cast<int*>(take(sizeof(int) * N));
+  w.G = take(N * d * E); w.Hrows = take(N * d * E); w.dH = take(N * d * E);
+  w.loss_fwd_bytes = adasoftmax_workspace_bytes(D->ada, static_cast<int>(N), false);
+  w.loss_fwd = take(w.loss_fwd_bytes);
+  w.loss_bwd_bytes = adasoftmax_bwd_workspace_bytes(D->ada, static_cast<int>(N));
+  w.loss_bwd = take(w.loss_bwd_bytes);
+  w.total = off;
+  return w;
+}
+
+// ------------------------------------------------------------------------------ small call helpers
+struct Ctx {
+  tnt_decoder* D;
+  cudaStream_t st;
+  int dt;
+  float* grad(const std::string& key) {
+    auto it = D->grads.find(key);
+    return it == D->grads.end() ? nullptr : it->second;
+  }
+  const float* raw(const std::string& key) {
+    auto it = D->raw.find(key);
+    return it == D->raw.end() ? nullptr : it->second.data;
+  }
+};
+
+int gemm(Ctx& c, int layout, int epi, const void* A, long lda, const void* W, long ldw, void* C, long ldc, int M, int N,
+         int K, int dt_out, const void* res = nullptr, long ldr = 0, const int* m_dyn = nullptr, float alpha = 0.f,
+         const float* bias = nullptr, int groups = 1, long sa = 0, long sw = 0, long sr = 0, long sc = 0) {
+  tnt_linear_params p = {};
+  p.a = A; p.lda = lda; p.w = W; p.ldw = ldw; p.c = C; p.ldc = ldc; p.residual = res; p.ldr = ldr; p.bias = bias;
+  p.M = M; p.N = N; p.K = K; p.m_dyn = m_dyn; p.groups = groups;
+  p.stride_a = sa; p.stride_w = sw; p.stride_res = sr; p.stride_c = sc;
+  p.dtype_in = c.dt; p.dtype_out = dt_out; p.epilogue = epi; p.layout = layout; p.alpha = alpha;
+  return launch_gemm(&p, -1, nullptr, nullptr, c.st);
+}
+
+int ln_bwd(Ctx& c, const void* x, long ldx, const void* dy, long lddy, void* dx, long lddx, const float* gamma,
+           float* dgamma, float* dbeta, int rows, int C) {
+  TNT_CHECK_ARG(dgamma && dbeta, "train: LayerNorm gradient buffer missing");
+  TNT_CUDA(cudaMemsetAsync(dgamma, 0, sizeof(float) * C, c.st));
+  TNT_CUDA(cudaMemsetAsync(dbeta, 0, sizeof(float) * C, c.st));
+  tnt_layernorm_bwd_params p = {};
+  p.x = x; p.ldx = ldx; p.dy = dy; p.lddy = lddy; p.dx = dx; p.lddx = lddx; p.gamma = gamma; p.dgamma = dgamma;
+  p.dbeta = dbeta; p.rows = rows; p.C = C; p.eps = 1e-5f; p.dtype = c.dt;
+  return tnt_layernorm_bwd(&p, c.st);
+}
+
+// gradient of a GehringLinear: dWp [rows(prepared order), cols] fp32 -> weight_v / weight_g (or plain weight)
+int linear_param_grads(Ctx& c, const std::string& prefix, const float* dWp, int rows, int cols, bool glu) {
+  const float* g = c.raw(prefix + "weight_g");
+  if (g) {
+    const float* v = c.raw(prefix + "weight_v");
+    float *dv = c.grad(prefix + "weight_v"), *dg = c.grad(prefix + "weight_g");
+    TNT_CHECK_ARG(v && dv && dg, "train: '%sweight_v/_g' parameter or gradient buffer missing", prefix.c_str());
+    return wn_bwd(v, g, dWp, cols, dv, dg, rows, cols, glu, c.st);
+  }
+  const float* v = c.raw(prefix + "weight");
+  float* dv = c.grad(prefix + "weight");
+  TNT_CHECK_ARG(v && dv, "train: '%sweight' parameter or gradient buffer missing", prefix.c_str());
+  return wn_bwd(v, nullptr, dWp, cols, dv, nullptr, rows, cols, glu, c.st);
+}
+
+int bias_grad(Ctx& c, const std::string& key, const void* dy, long ld, int M, int N, bool deinterleave, long offset = 0) {
+  float* g = c.grad(key);
+  TNT_CHECK_ARG(g, "train: gradient buffer for '%s' missing", key.c_str());
+  return colsum(dy, ld, M, N, nullptr, g + offset, c.dt, deinterleave, false, c.st);
+}
+
+inline const char* off(const void* p, size_t elems, size_t E) { return static_cast<const char*>(p) + elems * E; }
+inline char* off(void* p, size_t elems, size_t E) { return static_cast<char*>(p) + elems * E; }
+
+
+// ------------------------------------------------------------------------------ forward (activations kept)
+FwdWs layer_ws(const TrainWs& w, int l, int ns) {
+  FwdWs f = {};
+  const LayerAct& a = w.act[l];
+  f.X0 = a.X0; f.X1 = a.X1; f.h = a.h; f.logits = a.logits; f.cbuf = a.cbuf; f.ybuf = a.yc; f.ybuf2 = a.yf;
+  f.Q = a.Q; f.AO = a.AO; f.CAT = a.CATpre; f.CATln = a.CATln; f.F = a.F;
+  for (int s = 0; s < ns; ++s) f.kv[s] = w.kv[s];
+  return f;
+}
+
+tnt_xattn_params attn_params(const tnt_decoder* D, const tnt_contexts* ctx, const TrainWs& w, int l, int s) {
+  const tnt_decoder_config& c = D->cfg;
+  const int d = c.d, ns = c.n_sources, B = ctx->B, T = ctx->T;
+  const size_t E = D->esz();
+  const long ldkv = static_cast<long>(c.n_layers) * 2 * d;
+  const LayerAct& a = w.act[l];
+  tnt_xattn_params ap = {};
+  ap.q = off(a.Q, static_cast<size_t>(s) * d, E);
+  ap.q_stride_t = static_cast<long>(B) * ns * d; ap.q_stride_b = static_cast<long>(ns) * d;
+  ap.k = off(w.kv[s], static_cast<size_t>(l) * 2 * d, E);
+  ap.k_stride_s = static_cast<long>(B) * ldkv; ap.k_stride_b = ldkv;
+  ap.v = off(ap.k, d, E);
+  ap.v_stride_s = ap.k_stride_s; ap.v_stride_b = ap.k_stride_b;
+  ap.out = off(a.AO, static_cast<size_t>(s) * d, E);
+  ap.o_stride_t = ap.q_stride_t; ap.o_stride_b = ap.q_stride_b;
+  ap.mask = ctx->pad_mask[s]; ap.m_stride_b = ctx->S[s]; ap.m_stride_t = 0;
+  ap.mask_mode = (ctx->pad_mask[s] && ctx->S[s] > 0) ? TNT_MASK_KEY_PADDING : TNT_MASK_NONE;
+  ap.B = B; ap.T = T; ap.S = ctx->S[s] + 2; ap.H = c.heads; ap.D = d / c.heads; ap.n_extra = 0;
+  ap.mask_S = ctx->S[s];
+  ap.scale = 1.0f / sqrtf(static_cast<float>(d / c.heads));
+  ap.dtype = c.dtype;
+  return ap;
+}
+
+// ------------------------------------------------------------------------------ one layer, backward
+// in: gA = dL/dXout [N, d] (T x B order);  out: gA = dL/dXin
+int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xin) {
+  tnt_decoder* D = c.D;
+  const tnt_decoder_config& cf = D->cfg;
+  const LayerW& L = D->layers[l];
+  const LayerAct& a = w.act[l];
+  const int d = cf.d, ns = cf.n_sources, B = ctx->B, T = ctx->T, N = B * T, H = cf.heads, dt = c.dt, ffn = cf.ffn;
+  const int HK = H * L.K, ldl = D->ld_logits(L.K);
+  const long nsd = static_cast<long>(ns) * d;
+  const size_t E = D->esz();
+  const std::string p = "layers." + std::to_string(l) + ".";
+  // ---- final LayerNorm and feed-forward: Xout = LN(yf), yf = fc2(relu(fc1(X0))) + X0
+  TNT_TRY(ln_bwd(c, a.yf, d, w.gA, d, w.gB, d, L.ln_f_g, c.grad(p + "final_layer_norm.weight"),
+                 c.grad(p + "final_layer_norm.bias"), N, d));
+  TNT_TRY(gemm(c, TNT_NN, EPI_RELU_BWD, w.gB, d, L.wf2, ffn, w.dF, ffn, N, ffn, d, dt, a.F, ffn));
+  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.gB, d, a.F, ffn, w.dW, ffn, d, ffn, N, TNT_F32));
+  TNT_TRY(linear_param_grads(c, p + "fc2.", w.dW, d, ffn, false));
+  TNT_TRY(bias_grad(c, p + "fc2.bias", w.gB, d, N, d, false));
+  TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.dF, ffn, L.wf1, d, w.gC, d, N, d, ffn, dt, w.gB, d));      // gC = dX0
+  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.dF, ffn, a.X0, d, w.dW, d, ffn, d, N, TNT_F32));
+  TNT_TRY(linear_param_grads(c, p + "fc1.", w.dW, ffn, d, false));
+  TNT_TRY(bias_grad(c, p + "fc1.bias", w.dF, ffn, N, ffn, false));
+  // ---- context_fc over the concatenated, layer-normed per-source branches
+  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.gC, d, L.wc, nsd, w.dCAT, nsd, N, ns * d, d, dt));
+  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.gC, d, a.CATln, nsd, w.dW, nsd, d, ns * d, N, TNT_F32));
+  TNT_TRY(linear_param_grads(c, p + "context_fc.", w.dW, d, ns * d, false));
+  TNT_TRY(bias_grad(c, p + "context_fc.bias", w.gC, d, N, d, false));
+  for (int s = 0; s < ns; ++s) {
+    const std::string ln = p + "context_attn_lns." + cf.source_names[s] + ".";
+    TNT_TRY(ln_bwd(c, off(a.CATpre, static_cast<size_t>(s) * d, E), nsd, off(w.dCAT, static_cast<size_t>(s) * d, E), nsd,
+                   off(w.dCATp, static_cast<size_t>(s) * d, E), nsd, L.ln_src_g + s * d, c.grad(ln + "weight"),
+                   c.grad(ln + "bias"), N, d));
+  }
+  // ---- per-source attention branch: CATpre_s = out_proj_s(attn_s) + X1
+  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.dCATp, nsd, L.wo, d, w.dAO, nsd, N, d, d, dt, nullptr, 0, nullptr, 0.f, nullptr, ns,
+               d, static_cast<long>(d) * d, 0, d));
+  for (int s = 0; s < ns; ++s) {
+    const std::string at = p + "context_attns." + cf.source_names[s] + ".";
+    float* dwo = c.grad(at + "out_proj.weight");
+    TNT_CHECK_ARG(dwo, "train: gradient buffer for '%sout_proj.weight' missing", at.c_str());
+    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, off(w.dCATp, static_cast<size_t>(s) * d, E), nsd, off(a.AO, static_cast<size_t>(s) * d, E),
+                 nsd, dwo, d, d, d, N, TNT_F32));
+    TNT_TRY(bias_grad(c, at + "out_proj.bias", off(w.dCATp, static_cast<size_t>(s) * d, E), nsd, N, d, false));
+    XattnBwd xb;
+    xb.f = attn_params(D, ctx, w, l, s);
+    xb.dout = off(w.dAO, static_cast<size_t>(s) * d, E);
+    xb.dq = off(w.dQ, static_cast<size_t>(s) * d, E);
+    xb.dk = off(w.dkv[s], static_cast<size_t>(l) * 2 * d, E);
+    xb.dv = off(xb.dk, d, E);
+    xb.scratch = w.attn_scr;
+    TNT_TRY(xattn_bwd(&xb, c.st));
+    // query projection parameters of this source: q_proj_weight or rows [0, d) of in_proj_weight
+    float* dwq = c.grad(at + "in_proj_weight");
+    if (!dwq) dwq = c.grad(at + "q_proj_weight");
+    TNT_CHECK_ARG(dwq, "train: gradient buffer for the query projection of '%s' missing", at.c_str());
+    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, off(w.dQ, static_cast<size_t>(s) * d, E), nsd, a.X1, d, dwq, d, d, d, N, TNT_F32));
+    TNT_TRY(bias_grad(c, at + "in_proj_bias", off(w.dQ, static_cast<size_t>(s) * d, E), nsd, N, d, false));
+  }
+  // dX1 = dQ . Wq + sum_s dCATpre_s
+  TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.dQ, nsd, L.wq, d, w.gD, d, N, d, ns * d, dt, w.dCATp, nsd));
+  TNT_TRY(add_col_blocks(w.gD, d, w.dCATp, nsd, N, d, 1, ns, dt, c.st));
+  // ---- conv block: X1 = LN(yc), yc = linear2(conv(h)) + Xin, h = GLU(linear1(Xin))
+  TNT_TRY(ln_bwd(c, a.yc, d, w.gD, d, w.gB, d, L.ln_conv_g, c.grad(p + "conv_layer_norm.weight"),
+                 c.grad(p + "conv_layer_norm.bias"), N, d));                                          // gB = dyc
+  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.gB, d, L.w2, d, w.gC, d, N, d, d, dt));                         // gC = dcbuf
+  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.gB, d, a.cbuf, d, w.dW, d, d, d, N, TNT_F32));
+  TNT_TRY(linear_param_grads(c, p + "linear2.", w.dW, d, d, false));
+  TNT_TRY(bias_grad(c, p + "linear2.bias", w.gB, d, N, d, false));
+  {
+    tnt_dynconv_bwd_params bp = {};
+    bp.x = a.h; bp.ldx = d; bp.logits = a.logits; bp.ldl = ldl; bp.dy = w.gC; bp.lddy = d; bp.dx = w.gD; bp.lddx = d;
+    bp.dlogits = w.dlogits; bp.lddl = ldl; bp.T = T; bp.B = B; bp.C = d; bp.H = H; bp.K = L.K; bp.dtype = dt;
+    TNT_TRY(tnt_dynconv_bwd(&bp, c.st));                                                             // gD = dh (value path)
+  }
+  {
+    float* dwt = c.grad(p + "conv.weight_linear.weight");
+    TNT_CHECK_ARG(dwt, "train: gradient buffer for '%sconv.weight_linear.weight' missing", p.c_str());
+    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.dlogits, ldl, a.h, d, dwt, d, HK, d, N, TNT_F32));
+  }
+  TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.dlogits, ldl, L.wtap, d, w.gC, d, N, d, HK, dt, w.gD, d));   // gC = dh
+  TNT_TRY(gemm(c, TNT_NT, EPI_NONE, Xin, d, L.w1, d, w.raw, 2 * d, N, 2 * d, d, dt, nullptr, 0, nullptr, 0.f, L.b1));
+  TNT_TRY(glu_bwd(w.raw, 2 * d, w.gC, d, w.draw, 2 * d, N, d, dt, c.st));
+  TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.draw, 2 * d, L.w1, d, w.gA, d, N, d, 2 * d, dt, w.gB, d));    // gA = dXin
+  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.draw, 2 * d, Xin, d, w.dW, d, 2 * d, d, N, TNT_F32));
+  TNT_TRY(linear_param_grads(c, p + "linear1.", w.dW, 2 * d, d, true));
+  TNT_TRY(bias_grad(c, p + "linear1.bias", w.draw, 2 * d, N, 2 * d, true));
+  return TNT_OK;
+}
+
+
+// ------------------------------------------------------------------------------ K/V projection parameters
+int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int s) {
+  tnt_decoder* D = c.D;
+  const tnt_decoder_config& cf = D->cfg;
+  const int d = cf.d, Ls = cf.n_layers, kd = cf.source_dim[s], B = ctx->B, S = ctx->S[s];
+  const int ldkv = Ls * 2 * d;
+  const size_t E = D->esz();
+  // learned bias_k / bias_v row (key index S) of every layer
+  TNT_TRY(kv_extra_grad(w.dkv[s], ldkv, S, B, ldkv, w.vecs, c.dt, c.st));
+  for (int l = 0; l < Ls; ++l) {
+    const std::string at = "layers." + std::to_string(l) + ".context_attns." + cf.source_names[s] + ".";
+    float *gk = c.grad(at + "bias_k"), *gv = c.grad(at + "bias_v");
+    TNT_CHECK_ARG(gk && gv, "train: gradient buffer for '%sbias_k/v' missing", at.c_str());
+    TNT_CUDA(cudaMemcpyAsync(gk, w.vecs + static_cast<size_t>(l) * 2 * d, sizeof(float) * d, cudaMemcpyDeviceToDevice, c.st));
+    TNT_CUDA(cudaMemcpyAsync(gv, w.vecs + static_cast<size_t>(l) * 2 * d + d, sizeof(float) * d, cudaMemcpyDeviceToDevice, c.st));
+  }
+  // projection biases: column sums over the S*B memory rows
+  TNT_TRY(colsum(w.dkv[s], ldkv, S * B, ldkv, nullptr, w.vecs, c.dt, false, false, c.st));
+  // projection weights of all layers in one GEMM: dWkv [L*2d, kdim] = dKV^T . memory
+  if (S * B > 0) {
+    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.dkv[s], ldkv, ctx->memory[s], kd, w.dW, kd, ldkv, kd, S * B, TNT_F32));
+  } else {
+    TNT_CUDA(cudaMemsetAsync(w.dW, 0, sizeof(float) * ldkv * kd, c.st));
+  }
+  for (int l = 0; l < Ls; ++l) {
+    const std::string at = "layers." + std::to_string(l) + ".context_attns." + cf.source_names[s] + ".";
+    const float* src = w.dW + static_cast<size_t>(l) * 2 * d * kd;
+    float* gb = c.grad(at + "in_proj_bias");
+    TNT_CHECK_ARG(gb, "train: gradient buffer for '%sin_proj_bias' missing", at.c_str());
+    TNT_CUDA(cudaMemcpyAsync(gb + d, w.vecs + static_cast<size_t>(l) * 2 * d, sizeof(float) * 2 * d, cudaMemcpyDeviceToDevice, c.st));
+    if (float* gi = c.grad(at + "in_proj_weight")) {
+      TNT_CUDA(cudaMemcpyAsync(gi + static_cast<size_t>(d) * d, src, sizeof(float) * 2 * d * kd, cudaMemcpyDeviceToDevice, c.st));
+    } else {
+      float *gk = c.grad(at + "k_proj_weight"), *gv = c.grad(at + "v_proj_weight");
+      TNT_CHECK_ARG(gk && gv, "train: gradient buffer for '%sk/v_proj_weight' missing", at.c_str());
+      TNT_CUDA(cudaMemcpyAsync(gk, src, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, c.st));
+      TNT_CUDA(cudaMemcpyAsync(gv, src + static_cast<size_t>(d) * kd, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, c.st));
+    }
+  }
+  (void)E;
+  return TNT_OK;
+}
+
+// ------------------------------------------------------------------------------ embedding bands
+// out = table_i[id - lo_i] . proj_i^T * sqrt(d) + position (adaptive.py:61-76); gE = dL/d(out) [N, d] in T x B order.
+// Band tables are tied to the softmax output rows: their gradient buffers already hold the softmax part.
+int embed_bwd(Ctx& c, const int64_t* ids, int B, int T, TrainWs& w, const void* gE) {
+  tnt_decoder* D = c.D;
+  const tnt_decoder_config& cf = D->cfg;
+  const int d = cf.d, N = B * T, nb = cf.n_clusters;
+  const size_t E = D->esz();
+  int edges[TNT_MAX_CLUSTERS + 1];
+  edges[0] = 0;
+  for (int i = 0; i < nb; ++i) edges[i + 1] = cf.cutoffs[i];
+  TNT_CHECK_ARG(nb + 1 <= TNT_MAX_CLUSTERS, "train: embedding backward supports at most %d vocabulary bands", TNT_MAX_CLUSTERS - 1);
+  TNT_TRY(band_rows(ids, N, edges, nb, w.band_head, w.band_rows, w.band_loc, w.band_cnt, c.st));
+  const float sq = sqrtf(static_cast<float>(d));
+  for (int i = 0; i < nb; ++i) {
+    const std::string e = "embedder.token_embedder_adaptive.embeddings." + std::to_string(i);
+    const int di = D->emb_dim[i];
+    const float* table = c.raw(e + ".0.weight");
+    float *gt = c.grad(e + ".0.weight"), *gp = c.grad(e + ".1.weight");
+    TNT_CHECK_ARG(table && gt && gp, "train: embedding band %d parameter or gradient buffer missing", i);
+    const int* rows = w.band_rows + static_cast<long>(i) * N;
+    const int* loc = w.band_loc + static_cast<long>(i) * N;
+    const int* cnt = w.band_cnt + i;
+    TNT_CUDA(cudaMemsetAsync(w.G, 0, E * N * d, c.st));       // pad rows of the 64-row reduction blocks must be 0
+    TNT_CUDA(cudaMemsetAsync(w.Hrows, 0, E * N * d, c.st));
+    TNT_TRY(gather_rows(gE, d, rows, cnt, N, w.G, d, d, c.dt, B, T, c.st));
+    TNT_TRY(gather_table_rows(table, di, loc, cnt, N, w.Hrows, di, di, c.dt, c.st));
+    // d proj_i [d, dim_i] = sqrt(d) G^T . H
+    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.G, d, w.Hrows, di, gp, di, d, di, N, TNT_F32, nullptr, 0, cnt, sq));
+    // d H [rows, dim_i] = sqrt(d) G . proj_i, scattered into the band table (padding row 0 skipped)
+    TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.G, d, D->emb_proj[i], di, w.dH, di, N, di, d, c.dt, nullptr, 0, cnt, sq));
+    TNT_TRY(scatter_table_grad(w.dH, di, loc, cnt, N, gt, di, di, c.dt, c.st));
+  }
+  return TNT_OK;
+}
+
+}  // namespace
+}  // namespace tnt
+
+using namespace tnt;
+
+extern "C" size_t tnt_decoder_train_workspace_bytes(const tnt_decoder* d, int B, int T, const int* S) {
+  if (!d || !S) return 0;
+  return carve_train(d, B, T, S, nullptr).total;
+}
+
+extern "C" int tnt_decoder_set_grad(tnt_decoder* d, const char* key, float* grad) {
+  TNT_CHECK_ARG(d && key, "decoder_set_grad: bad arguments");
+  if (grad) d->grads[key] = grad;
+  else d->grads.erase(key);
+  return TNT_OK;
+}
+
+extern "C" int tnt_decoder_train_step(tnt_decoder* D, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,
+                                      float loss_scale, float* out2, void* workspace, size_t workspace_bytes,
+                                      tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized, "decoder_train_step: decoder not finalized");
+  TNT_CHECK_ARG(ids && target && ctx && out2 && workspace, "decoder_train_step: null pointer");
+  const tnt_decoder_config& cf = D->cfg;
+  const int B = ctx->B, T = ctx->T, N = B * T, d = cf.d, ns = cf.n_sources, Ls = cf.n_layers;
+  TNT_CHECK_ARG(B > 0 && T > 0, "decoder_train_step: empty batch");
+  TNT_CHECK_ARG(T + cf.pad_idx + 1 <= cf.max_positions, "decoder_train_step: T=%d exceeds the position table", T);
+  TNT_CHECK_ALIGN((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "decoder_train_step: workspace alignment");
+  TrainWs w = carve_train(D, B, T, ctx->S, workspace);
+  if (w.total > workspace_bytes) {
+    set_error("decoder_train_step: workspace %zu < %zu", workspace_bytes, w.total);
+    return TNT_ERR_WORKSPACE;
+  }
+  cudaStream_t st = as_stream(stream);
+  Ctx c{D, st, cf.dtype};
+  // ---------------- forward
+  {
+    FwdWs f0 = layer_ws(w, 0, ns);
+    TNT_TRY(project_kv(D, ctx, f0, st));
+  }
+  TNT_TRY(embed(D, ids, B, T, w.emb, nullptr, st));
+  for (int l = 0; l < Ls; ++l) {
+    FwdWs f = layer_ws(w, l, ns);
+    const void* xin = l == 0 ? w.emb : w.act[l - 1].Xout;
+    TNT_TRY(run_layer(D, l, ctx, f, xin, w.act[l].Xout, B, T, nullptr, nullptr, nullptr, false, st));
+  }
+  TNT_TRY(permute_rows(w.act[Ls - 1].Xout, w.Xbt, B, T, d, cf.dtype, false, st));     // T x B -> B x T rows
+  TNT_TRY(adasoftmax_nll(D->ada, w.Xbt, d, target, N, cf.pad_idx, out2, w.loss_fwd, w.loss_fwd_bytes, st));
+  // ---------------- backward: loss
+  const int nt = cf.n_clusters - 1;
+  float* d_proj[TNT_MAX_CLUSTERS] = {};
+  float* d_out[TNT_MAX_CLUSTERS] = {};
+  float* d_words = c.grad("embedder.token_embedder_adaptive.embeddings.0.0.weight");
+  float* d_class = nt > 0 ? c.grad("adaptive_softmax.head.class_proj.weight") : nullptr;
+  TNT_CHECK_ARG(d_words && (nt == 0 || d_class), "decoder_train_step: gradient buffers of the softmax head missing");
+  for (int i = 0; i < nt; ++i) {
+    d_proj[i] = c.grad("adaptive_softmax.tail." + std::to_string(i) + ".0.weight");
+    d_out[i] = c.grad("embedder.token_embedder_adaptive.embeddings." + std::to_string(i + 1) + ".0.weight");
+    TNT_CHECK_ARG(d_proj[i] && d_out[i], "decoder_train_step: gradient buffers of softmax tail %d missing", i);
+  }
+  TNT_TRY(adasoftmax_nll_bwd(D->ada, w.Xbt, d, N, cf.pad_idx, loss_scale, w.loss_fwd, w.dXbt, d, d_words, d_class, d_proj,
+                             d_out, w.loss_bwd, w.loss_bwd_bytes, st));
+  TNT_TRY(permute_rows(w.dXbt, w.gA, B, T, d, cf.dtype, true, st));                    // B x T -> T x B rows
+  // ---------------- backward: layers, K/V projections, embedding
+  for (int l = Ls - 1; l >= 0; --l) {
+    const void* xin = l == 0 ? w.emb : w.act[l - 1].Xout;
+    TNT_TRY(layer_bwd(c, ctx, w, l, xin));
+  }
+  for (int s = 0; s < ns; ++s) TNT_TRY(kv_param_grads(c, ctx, w, s));
+  TNT_TRY(embed_bwd(c, ids, B, T, w, w.gA));
+  return TNT_OK;
+}

@@ -153,11 +153,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint32_t v[32];
         ptx::tmem_ld_32x32(taddr + c * 32, v);
         ptx::tmem_ld_wait();
-        if (EPI == EPI_SMGRAD && row >= M && row < g.M) {       // pad rows of a dynamic-M problem: zeros
-          float z[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) z[i] = 0.f;
-          epilogue_store<EPI_NONE, TOut, 32>(g, grp, row, n0, z);
+        if (EPI != EPI_LSE && EPI != EPI_GLU && g.m_dyn && !g.a_mn && row >= M && row < g.M) {
+          // pad rows of a dynamic-M problem get zeros: a later TN GEMM reduces over whole 64-row blocks
+          zero_store<TOut, 32>(g, grp, row, n0);
         }
         if (row < M) {
           float acc[32];
@@ -212,7 +210,7 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(GemmArgs g) {
   const int M = g.a_mn ? g.M : min(g.M, dyn);
   const int Kred = g.a_mn ? min(g.K, dyn) : g.K;
   const int m0 = blockIdx.y * TM, n0 = blockIdx.x * TN;
-  if (m0 >= M && !(EPI == EPI_SMGRAD && m0 < g.M && m0 < ((M + 127) & ~127))) return;
+  if (m0 >= M && !(EPI != EPI_LSE && EPI != EPI_GLU && g.m_dyn && !g.a_mn && m0 < g.M && m0 < ((M + 127) & ~127))) return;
   const TIn* A = reinterpret_cast<const TIn*>(g.a) + grp * g.sa;
   const TIn* W = reinterpret_cast<const TIn*>(g.w) + grp * g.sw;
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
@@ -280,9 +278,8 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(GemmArgs g) {
             make_float4(la.m, la.s, __int_as_float(la.arg), la.tz);
     } else if (row < M) {
       epilogue_store<EPI, TOut, 4>(g, grp, row, n0 + tx * 4, acc[i]);
-    } else if (EPI == EPI_SMGRAD && row < g.M) {
-      float z[4] = {0.f, 0.f, 0.f, 0.f};
-      epilogue_store<EPI_NONE, TOut, 4>(g, grp, row, n0 + tx * 4, z);
+    } else if (EPI != EPI_LSE && EPI != EPI_GLU && g.m_dyn && !g.a_mn && row < g.M) {
+      zero_store<TOut, 4>(g, grp, row, n0 + tx * 4);
     }
   }
 }

@@ -120,6 +120,15 @@ __device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m
   }
 }
 
+// zeros into columns [n0, n0+NC) of output row m (pad rows of a dynamic-M problem)
+template <typename TOut, int NC>
+__device__ __forceinline__ void zero_store(const GemmArgs& g, int grp, int m, int n0) {
+  TOut* crow = reinterpret_cast<TOut*>(g.c) + grp * g.sc + static_cast<long>(m) * g.ldc;
+#pragma unroll
+  for (int i = 0; i < NC; ++i)
+    if (n0 + i < g.N) crow[n0 + i] = from_f<TOut>(0.f);
+}
+
 // running (max, sumexp, argmax, target-logit) over a run of columns of one row
 struct LseAcc {
   float m, s, tz;

@@ -170,7 +170,7 @@ class DynamicConvDecoder(nn.Module):
             self._weights = torch.empty(nbytes, dtype=torch.uint8, device='cuda')
             _lib.check(L.tnt_decoder_bind_weights(self._handle, _ptr(self._weights), nbytes), 'bind_weights')
         keep = []
-        for k, p in self.named_parameters():
+        for k, p in self.named_parameters(remove_duplicate=False):
             t = p.detach().contiguous()
             keep.append(t)
             shp = (C.c_int64 * t.dim())(*t.shape)
@@ -288,6 +288,74 @@ class DynamicConvDecoder(nn.Module):
             n = steps.value
             return lp[:, :n], ids[:, :n + 1]
         return lp, ids
+
+    # ------------------------------------------------------------------ training (kernel group 4)
+    def tied_keys(self):
+        """Output-softmax rows tied to the embedding bands (softmax.py:83-86,111-132): alias -> owner."""
+        e = 'embedder.token_embedder_adaptive.embeddings.%d.0.weight'
+        ties = {'adaptive_softmax.head.word_proj.weight': e % 0}
+        for i in range(len(self.cutoffs) - 1):
+            ties['adaptive_softmax.tail.%d.2.weight' % i] = e % (i + 1)
+        return ties
+
+    def enable_training(self):
+        """Ties the output rows to the embedding bands (one Parameter, as in the reference), moves every
+        trainable parameter into ONE flat fp32 arena with a matching flat gradient arena (`flat_params`,
+        `flat_grads`; `.grad` of each parameter is a view), and registers the gradient buffers with the engine.
+        The flat gradient arena is what data-parallel training all-reduces (one NCCL call per bucket)."""
+        if getattr(self, 'flat_params', None) is not None:
+            return self
+        own = dict(self.named_parameters(remove_duplicate=False))
+        for alias, owner in self.tied_keys().items():
+            mod = self
+            parts = alias.split('.')
+            for q in parts[:-1]:
+                mod = getattr(mod, q)
+            mod._parameters[parts[-1]] = own[owner]
+        named = [(k, p) for k, p in self.named_parameters() if 'token_embedder_position' not in k]
+        total = sum((p.numel() + 63) // 64 * 64 for _, p in named)
+        self.flat_params = torch.empty(total, dtype=torch.float32, device='cuda')
+        self.flat_grads = torch.zeros(total, dtype=torch.float32, device='cuda')
+        self.param_slices = {}
+        off = 0
+        L = _lib.lib()
+        with torch.no_grad():
+            for k, p in named:
+                n = p.numel()
+                view = self.flat_params[off:off + n].view(p.shape)
+                view.copy_(p.data)
+                p.data = view
+                p.requires_grad_(True)
+                p.grad = self.flat_grads[off:off + n].view(p.shape)
+                self.param_slices[k] = (off, n)
+                off += (n + 63) // 64 * 64
+        self._dirty = True
+        h = self._h()
+        for k, p in named:
+            _lib.check(L.tnt_decoder_set_grad(h, k.encode(), _ptr(p.grad)), 'tnt_decoder_set_grad ' + k)
+        return self
+
+    def mark_updated(self):
+        """Call after the optimizer changed the parameters: the prepared (folded, cast) weights are rebuilt."""
+        self._dirty = True
+
+    def train_step(self, prev_target, target, contexts, loss_scale=1.0):
+        """Forward + AdaptiveLoss + backward.  Gradients of `loss_scale * sum-NLL` are written into `.grad`
+        of every parameter (views of `flat_grads`).  Returns a device tensor [loss_sum, n_non_pad]."""
+        if getattr(self, 'flat_params', None) is None:
+            self.enable_training()
+        ids = prev_target['roberta'] if isinstance(prev_target, dict) else prev_target
+        ids = ids.to('cuda', torch.long).contiguous()
+        target = target.to('cuda', torch.long).contiguous()
+        B, T = ids.shape
+        L, h = _lib.lib(), self._h()
+        ctx, keep = self._contexts(contexts, B, T)
+        S = (C.c_int * 4)(*[ctx.S[i] for i in range(4)])
+        ws = self._workspace('train', L.tnt_decoder_train_workspace_bytes(h, B, T, S))
+        out = torch.empty(2, dtype=torch.float32, device='cuda')
+        _lib.check(L.tnt_decoder_train_step(h, _ptr(ids), _ptr(target), C.byref(ctx), float(loss_scale), _ptr(out),
+                                            _ptr(ws), ws.numel(), _stream()), 'tnt_decoder_train_step')
+        return out
 
     def score_host(self, ids_host, target_host, contexts_host):
         """End-to-end teacher-forced scoring from PINNED HOST buffers (ids/targets int64 [B,T], contexts in

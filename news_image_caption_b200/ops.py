@@ -181,6 +181,38 @@ def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=No
     return out, w
 
 
+def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=0):
+    """Backward of `xattn` (n_extra = 0: extra rows are ordinary k / v rows).  Returns (dq, dk, dv)."""
+    q, k, v, out, dout = [_cuda(t).contiguous() for t in (q, k, v, out, dout)]
+    T, B, E = q.shape
+    S = k.shape[0]
+    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    bp = _lib.XattnBwdParams()
+    p = bp.fwd
+    p.q, p.q_stride_t, p.q_stride_b = q.data_ptr(), B * E, E
+    p.k, p.k_stride_s, p.k_stride_b = k.data_ptr(), B * E, E
+    p.v, p.v_stride_s, p.v_stride_b = v.data_ptr(), B * E, E
+    p.out, p.o_stride_t, p.o_stride_b = out.data_ptr(), B * E, E
+    keep = []
+    p.mask_mode = MASK_NONE
+    if pad_mask is not None:
+        m = pad_mask.to(torch.bool).contiguous()
+        keep.append(m)
+        p.mask, p.m_stride_b, p.m_stride_t, p.mask_mode, p.mask_S = m.data_ptr(), m.shape[1], 0, MASK_KEY_PADDING, mask_S
+    elif v2_mask is not None:
+        m = v2_mask.to(torch.bool).expand(B, v2_mask.shape[1], S).contiguous()
+        keep.append(m)
+        p.mask, p.m_stride_b, p.mask_mode = m.data_ptr(), m.shape[1] * S, MASK_V2
+        p.m_stride_t = S if m.shape[1] > 1 else 0
+    p.B, p.T, p.S, p.H, p.D, p.n_extra, p.scale, p.dtype = B, T, S, H, E // H, 0, scale, _code(q)
+    L = _lib.lib()
+    scr = torch.empty(L.tnt_xattn_bwd_scratch_bytes(B, T, H, E // H) + 256, dtype=torch.uint8, device=q.device)
+    bp.dout, bp.dq, bp.dk, bp.dv = dout.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr()
+    bp.scratch, bp.scratch_bytes = scr.data_ptr(), scr.numel()
+    _lib.check(L.tnt_xattn_bwd(C.byref(bp), _st()), 'tnt_xattn_bwd')
+    return dq, dk, dv
+
+
 def lse(x, w, bias=None, target=None):
     """Row statistics of z = x @ w^T (+bias) without materialising z:
     returns (max, sumexp, argmax, target_logit) as tensors [M]."""

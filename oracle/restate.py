@@ -197,13 +197,41 @@ def embed(ids: torch.Tensor, sd: SD, cutoffs: Sequence[int], start_pos: int = 0,
         if m.any():
             e = sd[p + 'token_embedder_adaptive.embeddings.%d.0.weight' % i]
             pr = sd[p + 'token_embedder_adaptive.embeddings.%d.1.weight' % i]
-            out[m] = F.linear(e[ids[m] - lo], pr)
+            # nn.Embedding(padding_idx=0): band-local row 0 receives no gradient from this path (adaptive.py:42,51)
+            out[m] = F.linear(F.embedding(ids[m] - lo, e, padding_idx=0), pr)
         lo = hi
     out = out * math.sqrt(d)
     tab = sd[p + 'token_embedder_position.weights']
     pos = torch.arange(T)[None, :].expand(B, T) + 2 + start_pos
     pos = torch.where(ids == 1, torch.ones_like(pos), pos)
     return out + tab[pos]
+
+
+def tied_output_keys(n_clusters: int) -> Dict[str, str]:
+    """alias -> owner of the tied output rows (tie_adaptive_weights, softmax.py:83-86,111-132)."""
+    e = 'embedder.token_embedder_adaptive.embeddings.%d.0.weight'
+    ties = {'adaptive_softmax.head.word_proj.weight': e % 0}
+    for i in range(n_clusters - 1):
+        ties['adaptive_softmax.tail.%d.2.weight' % i] = e % (i + 1)
+    return ties
+
+
+def leaf_state_dict(sd: SD, ties: Optional[Dict[str, str]] = None) -> SD:
+    """Differentiable copy of a state_dict that keeps parameter TYING: entries sharing storage in `sd`
+    (the tied embedding / output rows, softmax.py:83-86,111-132) share one leaf, so autograd sums their
+    gradients exactly as the reference module does."""
+    leaves, out = {}, {}
+    for k, v in sd.items():
+        if not torch.is_tensor(v) or not v.is_floating_point():
+            out[k] = v
+            continue
+        key = (v.data_ptr(), tuple(v.shape))
+        if key not in leaves:
+            leaves[key] = v.detach().clone().requires_grad_(True)
+        out[k] = leaves[key]
+    for alias, owner in (ties or {}).items():       # fixtures saved from a state_dict lose the storage sharing
+        out[alias] = out[owner]
+    return out
 
 
 # ----------------------------------------------------------------------------- adaptive softmax

@@ -1,0 +1,113 @@
+"""GPU parity of the backward kernels and the training step (north_star kernel group 4) against autograd
+through the oracle (oracle/restate.py is plain differentiable torch; its gradients are pinned against the
+reference modules' own autograd in tests/test_oracle_vs_reference.py)."""
+import os
+
+import pytest
+import torch
+
+from oracle import restate as O
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), 'golden')
+
+
+def rel_err(a, b):
+    a, b = a.float().cpu(), b.float().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+
+
+def l2_err(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
+
+
+@pytest.fixture(scope='module')
+def ops():
+    from news_image_caption_b200 import build, _lib, ops as o
+    build.build()
+    _lib.require_device()
+    return o
+
+
+@pytest.mark.parametrize('T,S,H,D,mode', [(7, 20, 4, 16, 'pad'), (32, 130, 2, 64, 'pad'), (40, 33, 2, 128, 'causal'),
+                                          (5, 9, 2, 64, 'none')])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_xattn_backward(ops, T, S, H, D, mode, dtype):
+    g = torch.Generator().manual_seed(T * 100 + S)
+    B, E = 3, H * D
+    q = torch.randn(T, B, E, generator=g).to(dtype)
+    k = torch.randn(S, B, E, generator=g).to(dtype)
+    v = torch.randn(S, B, E, generator=g).to(dtype)
+    do = torch.randn(T, B, E, generator=g).to(dtype)
+    scale = D ** -0.5
+    pad = v2 = None
+    qd, kd, vd = [t.double().requires_grad_(True) for t in (q, k, v)]
+    s = torch.einsum('tbhd,sbhd->bhts', qd.view(T, B, H, D), kd.view(S, B, H, D)) * scale
+    if mode == 'pad':
+        pad = torch.rand(B, S, generator=g) > 0.6
+        pad[:, -2:] = False                       # the two extra keys are never masked
+        pad[0, :-2] = True                        # a fully masked source
+        s = s.masked_fill(pad[:, None, None, :], float('-inf'))
+    elif mode == 'causal':
+        v2 = torch.tril(torch.ones(T, S)).bool()[None]
+        s = s.masked_fill(~v2[:, None], -1e9)
+    o = torch.einsum('bhts,sbhd->tbhd', torch.softmax(s, -1), vd.view(S, B, H, D)).reshape(T, B, E)
+    gq, gk, gv = torch.autograd.grad(o, [qd, kd, vd], do.double())
+    out, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, scale, pad_mask=None if pad is None else pad.cuda(),
+                       v2_mask=None if v2 is None else v2.cuda(), mask_S=S - 2 if pad is not None else 0)
+    dq, dk, dv = ops.xattn_bwd(q.cuda(), k.cuda(), v.cuda(), out, do.cuda(), H, scale,
+                               pad_mask=None if pad is None else pad.cuda(),
+                               v2_mask=None if v2 is None else v2.cuda(), mask_S=S - 2 if pad is not None else 0)
+    tol = 2e-5 if dtype == torch.float32 else 3e-2
+    assert rel_err(out, o.detach()) < tol
+    assert rel_err(dq, gq) < tol and rel_err(dk, gk) < tol and rel_err(dv, gv) < tol
+
+
+def make_decoder(cfg, sd, dtype):
+    from news_image_caption_b200 import DynamicConvDecoder, build
+    build.build()
+    dec = DynamicConvDecoder(decoder_output_dim=cfg['d'], decoder_attention_heads=cfg['heads'],
+                             decoder_ffn_embed_dim=cfg['ffn'], decoder_kernel_size_list=cfg['kernels'],
+                             vocab_size=cfg['vocab'], adaptive_softmax_cutoff=cfg['cutoffs'][:-1],
+                             sources=cfg['sources'], dtype=dtype)
+    dec.load_reference_state_dict(sd)
+    return dec
+
+
+def oracle_grads(f, scale):
+    cfg = f['config']
+    sd = O.leaf_state_dict(f['state_dict'], O.tied_output_keys(len(cfg['cutoffs'])))
+    X, _ = O.decoder_forward(f['prev'], f['contexts'], sd, cfg['heads'], cfg['cutoffs'], cfg['sources'])
+    loss, n = O.adaptive_nll(X, f['target'], sd, cfg['cutoffs'])
+    (loss * scale).backward()
+    return loss.detach(), n, sd
+
+
+@pytest.mark.parametrize('name', ['tell2_small.pt', 'tell4_small.pt'])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_train_step_gradients(name, dtype):
+    f = torch.load(os.path.join(G, name), weights_only=False)
+    scale = 0.37
+    loss_o, n_o, sd = oracle_grads(f, scale)
+    dec = make_decoder(f['config'], f['state_dict'], dtype).enable_training()
+    ctx = {k: v.cuda() for k, v in f['contexts'].items()}
+    out = dec.train_step(f['prev'].cuda(), f['target'].cuda(), ctx, loss_scale=scale)
+    torch.cuda.synchronize()
+    tol = 1e-4 if dtype == torch.float32 else 2e-2
+    assert int(out[1].item()) == n_o
+    assert abs(out[0].item() - loss_o.item()) < tol * abs(loss_o.item())
+    # fp32: max-norm relative error per tensor; bf16 (activation gradients are stored in bf16 through
+    # 2 layers x ~15 ops): relative L2 error per tensor -- north_star states tolerances for logits / loss only
+    gtol = 2e-4 if dtype == torch.float32 else 1e-1
+    err = rel_err if dtype == torch.float32 else l2_err
+    worst = []
+    for k, p in dec.named_parameters():
+        if 'token_embedder_position' in k:
+            continue
+        go = sd[k].grad
+        assert go is not None, k
+        worst.append((err(p.grad, go), k))
+    worst.sort(reverse=True)
+    assert worst[0][0] < gtol, '\n'.join('%.3e %s' % w for w in worst[:12])

@@ -57,6 +57,29 @@ def test_gradients_match_reference():
         close(a, b, 2e-4)
 
 
+@pytest.mark.parametrize('nsrc,srcs', [(2, ('image', 'article')), (4, ('image', 'article', 'faces', 'obj'))])
+def test_all_gradients_match_reference(nsrc, srcs):
+    """Every trainable parameter, with the tied embedding / output rows sharing one leaf and the
+    band-local padding rows (ids 0, cutoff[0], cutoff[1]) present in the batch."""
+    R = ri.load_tell()
+    dec = ri.build_ref_decoder(nsrc, d=32, heads=4, ffn=48, kernels=(3, 7), vocab=300, cutoff=(100, 200), seed=7)
+    prev, tgt, ctx = synth.make_batch(4, 9, 300, srcs, seed=11, S_img=3, S_art=10, S_obj=4)
+    prev[1, 3], prev[2, 4] = 100, 200                      # local row 0 of bands 1 and 2
+    X, _ = dec({'roberta': prev}, ctx)
+    loss, _ = R.AdaptiveLoss(1)(dec.adaptive_softmax, (X, None), tgt)
+    params = dict(dec.named_parameters())
+    g_ref = dict(zip(params, torch.autograd.grad(loss, list(params.values()), allow_unused=True)))
+    sd = O.leaf_state_dict(dec.state_dict())
+    Xo, _ = O.decoder_forward(prev, ctx, sd, 4, [100, 200, 300], srcs)
+    lo, _ = O.adaptive_nll(Xo, tgt, sd, [100, 200, 300])
+    for name, gr in g_ref.items():
+        if gr is None:
+            continue
+        go, = torch.autograd.grad(lo, sd[name], retain_graph=True, allow_unused=True)
+        assert go is not None, name
+        close(go, gr, 2e-4)
+
+
 def test_v2_other_variant():
     torch.set_grad_enabled(False)
     tv = ri.load_final_v2('final_roberta2')
