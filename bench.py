@@ -146,6 +146,8 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--workload', default='fwd', choices=['fwd', 'train'],
+                    help='fwd = BASELINE configs[1] (the default, driver-run line); train = configs[2] (fwd+bwd+allreduce+BertAdam)')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
@@ -182,7 +184,14 @@ def main():
     ctx_h = {k: pin(v.bfloat16() if v.is_floating_point() else v) for k, v in ctx.items()}
     h2d = prev_h.numel() * 8 * 2 + sum(v.numel() * v.element_size() for v in ctx_h.values())
 
+    trainer = None
+    if args.workload == 'train':
+        from news_image_caption_b200.trainer import Trainer
+        trainer = Trainer(dec, t_total=100000)
+
     def step():
+        if trainer is not None:
+            return trainer.step(prev_d, tgt_d, ctx_d)
         X, _ = dec(prev_d, ctx_d, need_attn=False)
         return dec.nll(X, tgt_d)
 
@@ -225,20 +234,34 @@ def main():
     # ---- end to end: pinned host buffers -> C ABI (H2D + forward + loss + D2H of the loss), every step.
     # Two batches are in flight (submit step i+1, then wait for step i): the H2D copies of one batch overlap
     # the compute of the other; every step still copies all of its inputs from pinned host memory.
-    for _ in range(2):
-        dec.score_host(prev_h, tgt_h, ctx_h)
-    sync_all()
-    t0 = time.perf_counter()
-    dec.score_host_submit(0, prev_h, tgt_h, ctx_h)
-    for i in range(1, args.steps):
-        dec.score_host_submit(i & 1, prev_h, tgt_h, ctx_h)
-        l_h, n_h = dec.score_host_wait((i - 1) & 1)
-    l_h, n_h = dec.score_host_wait((args.steps - 1) & 1)
+    if trainer is not None:
+        def e2e_step():
+            c = {k: v.cuda(non_blocking=True) for k, v in ctx_h.items()}
+            o = trainer.step(prev_h.cuda(non_blocking=True), tgt_h.cuda(non_blocking=True), c)
+            return o.cpu()
+        for _ in range(2):
+            e2e_step()
+        sync_all()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            o = e2e_step()
+        l_h, n_h = float(o[0]), float(o[1]) / world
+        loss_check = torch.tensor([l_h])         # parameters move every step: nothing to compare against
+    else:
+        for _ in range(2):
+            dec.score_host(prev_h, tgt_h, ctx_h)
+        sync_all()
+        t0 = time.perf_counter()
+        dec.score_host_submit(0, prev_h, tgt_h, ctx_h)
+        for i in range(1, args.steps):
+            dec.score_host_submit(i & 1, prev_h, tgt_h, ctx_h)
+            l_h, n_h = dec.score_host_wait((i - 1) & 1)
+        l_h, n_h = dec.score_host_wait((args.steps - 1) & 1)
     e2e_s = torch.tensor([time.perf_counter() - t0], device='cuda')
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = ntok_all.item() * args.steps / e2e_s.item()
-    assert abs(l_h - loss_check[0].item()) < 1e-3 * abs(l_h) and int(n_h) == ntok, (l_h, loss_check, n_h, ntok)
+    assert trainer is not None or (abs(l_h - loss_check[0].item()) < 1e-3 * abs(l_h) and int(n_h) == ntok), (l_h, loss_check, n_h, ntok)
 
     if rank != 0:
         if world > 1:
@@ -272,7 +295,7 @@ def main():
         'metric': 'decoder_tokens_per_sec', 'value': value, 'unit': 'tokens/s', 'n_gpus': world, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': ms_total / args.steps, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
-        'config': {'workload': WORKLOAD, 'l2': 'per-step working set (K/V 0.5 GB + activations) exceeds the 126 MB L2',
+        'config': {'workload': WORKLOAD if trainer is None else WORKLOAD.replace('fwd+adaptive-loss', 'TRAIN fwd+bwd+grad-allreduce+BertAdam'), 'l2': 'per-step working set (K/V 0.5 GB + activations) exceeds the 126 MB L2',
                    'non_pad_tokens_per_step_per_gpu': ntok},
         'captions_per_sec': B_PER_GPU * world * args.steps / (ms_total * 1e-3),
         'e2e': {'value': e2e_value, 'unit': 'tokens/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 8,

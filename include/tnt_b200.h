@@ -210,6 +210,7 @@ typedef struct {
   float scale;
   int dtype;
   int mask_S;         /* the mask covers keys [0, mask_S); 0 = all S (trailing k/v rows are then never masked) */
+  float* lse;         /* optional [B, H, T] fp32: log-sum-exp of the scaled, masked scores (saved for the backward) */
 } tnt_xattn_params;
 int tnt_xattn_fwd(const tnt_xattn_params* p, tnt_stream stream);
 
@@ -336,6 +337,29 @@ int tnt_decoder_set_grad(tnt_decoder* d, const char* key, float* grad);
 int tnt_decoder_train_step(tnt_decoder* d, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,
                            float loss_scale, float* out2, void* workspace, size_t workspace_bytes,
                            tnt_stream stream);
+
+/* Overlapping the gradient exchange with the backward pass: the step completes its gradients in stages --
+ * stage 0: softmax-only parameters (class_proj, tail projections); stage 1+i: every parameter of layer
+ * (n_layers-1-i); last stage: the embedding bands (tied output rows).  After tnt_decoder_train_step has been
+ * issued, tnt_decoder_stream_wait_stage makes `stream` wait (device side, no host sync) until that stage's
+ * gradient buffers are final, so a communication stream can all-reduce them while earlier layers still run. */
+int tnt_decoder_train_stages(const tnt_decoder* d);
+int tnt_decoder_stream_wait_stage(tnt_decoder* d, int stage, tnt_stream stream);
+
+/* Fused BertAdam step over flat fp32 arenas (the reference's optimizer: config.yaml:126-136, `bert_adam`):
+ * g' = grad_scale * (*grad_scale_dev) * g, clipped PER PARAMETER TENSOR to max_grad_norm (segments),
+ * m = b1 m + (1-b1) g', v = b2 v + (1-b2) g'^2, p -= lr * (m / (sqrt(v) + eps) + weight_decay * p).
+ * Arena segments start at multiples of 64 elements; seg_of_chunk[i] is the segment of elements [64i, 64i+64). */
+typedef struct {
+  float* params; const float* grads; float* m; float* v;
+  int64_t n;                       /* arena length, multiple of 64 */
+  const int* seg_of_chunk;         /* [n / 64] or NULL when max_grad_norm <= 0 */
+  float* seg_sq; int n_segments;   /* scratch [n_segments] */
+  const float* grad_scale_dev;     /* optional device scalar multiplied into the gradients (e.g. 1 / n_tokens) */
+  float grad_scale;                /* host scalar, 0 means 1 */
+  float max_grad_norm, lr, beta1, beta2, eps, weight_decay;
+} tnt_adam_params;
+int tnt_bert_adam_step(const tnt_adam_params* p, tnt_stream stream);
 
 /* End-to-end convenience used for the e2e benchmark: ids/targets/contexts/masks in PINNED HOST
  * memory, loss read back; performs the H2D copies, forward, loss and D2H on `stream` and

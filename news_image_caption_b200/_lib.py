@@ -63,12 +63,18 @@ class XattnParams(C.Structure):
                 ('k_stride_b', i64), ('v', vp), ('v_stride_s', i64), ('v_stride_b', i64), ('out', vp),
                 ('o_stride_t', i64), ('o_stride_b', i64), ('mask', vp), ('m_stride_b', i64), ('m_stride_t', i64),
                 ('bias_k', vp), ('bias_v', vp), ('weights', vp), ('B', i32), ('T', i32), ('S', i32), ('H', i32),
-                ('D', i32), ('n_extra', i32), ('mask_mode', i32), ('scale', f32), ('dtype', i32), ('mask_S', i32)]
+                ('D', i32), ('n_extra', i32), ('mask_mode', i32), ('scale', f32), ('dtype', i32), ('mask_S', i32), ('lse', vp)]
 
 
 class XattnBwdParams(C.Structure):
     _fields_ = [('fwd', XattnParams), ('dout', vp), ('dq', vp), ('dk', vp), ('dv', vp), ('scratch', vp),
                 ('scratch_bytes', C.c_size_t)]
+
+
+class AdamParams(C.Structure):
+    _fields_ = [('params', vp), ('grads', vp), ('m', vp), ('v', vp), ('n', i64), ('seg_of_chunk', vp), ('seg_sq', vp),
+                ('n_segments', i32), ('grad_scale_dev', vp), ('grad_scale', f32), ('max_grad_norm', f32), ('lr', f32),
+                ('beta1', f32), ('beta2', f32), ('eps', f32), ('weight_decay', f32)]
 
 
 class LseParams(C.Structure):
@@ -132,6 +138,9 @@ _SIGS = {
     'tnt_decoder_train_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
     'tnt_decoder_set_grad': (i32, [vp, C.c_char_p, vp]),
     'tnt_decoder_train_step': (i32, [vp, vp, vp, C.POINTER(Contexts), f32, vp, vp, C.c_size_t, vp]),
+    'tnt_decoder_train_stages': (i32, [vp]),
+    'tnt_decoder_stream_wait_stage': (i32, [vp, i32, vp]),
+    'tnt_bert_adam_step': (i32, [C.POINTER(AdamParams), vp]),
     'tnt_debug_force_simt_gemm': (None, [i32]),
     'tnt_debug_force_simt_attention': (None, [i32]),
 }

@@ -167,6 +167,8 @@ __global__ void __launch_bounds__(kThreads) xattn_fwd_kernel(tnt_xattn_params p)
   for (int qi = 0; qi < kQW; ++qi) {
     if (qi < nq) {
       const float inv = l[qi] > 0.f ? 1.f / l[qi] : 0.f;
+      if (p.lse && lane == 0)
+        p.lse[(static_cast<long>(b) * p.H + h) * p.T + t0 + qw + qi] = l[qi] > 0.f ? m[qi] + __logf(l[qi]) : INFINITY;
       T* o = op + static_cast<long>(t0 + qw + qi) * p.o_stride_t + static_cast<long>(b) * p.o_stride_b + h * D;
 #pragma unroll
       for (int dd = 0; dd < kMaxDD; ++dd)

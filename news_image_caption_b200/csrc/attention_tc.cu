@@ -35,6 +35,7 @@ constexpr uint32_t O_COL = 448;
 constexpr int SMEM_BYTES = Q_BYTES + KS * KV_STAGE + VS * KV_STAGE + PS * P_STAGE + 4096 + 2048;
 
 struct Args {
+  float* lse; float scale;
   const uint8_t* mask; long m_stride_b;
   void* out; long o_stride_t, o_stride_b;
   int B, T, S, H, mask_S;
@@ -219,10 +220,12 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       red_max[lane] = mine;
       named_bar(1 + hd, 128);
+      float col_max;                     // max of the unscaled scores of column (query) `lane`
       {
         const float* rm = red + hd * 128;
         const float m4 = fmaxf(fmaxf(rm[lane], rm[32 + lane]), fmaxf(rm[64 + lane], rm[96 + lane]));
         const float ms = (m4 == -INFINITY) ? 0.f : m4;
+        col_max = ms;
 #pragma unroll
         for (int c = 0; c < 32; ++c) mx[c] = __shfl_sync(0xffffffffu, ms, c) * a.scale_log2e;
       }
@@ -269,6 +272,12 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       red_sum[lane] = mysum;
       named_bar(3, 256);                 // the epilogue reads the sums of BOTH head groups
+      if (a.lse && quad == 0) {          // log-sum-exp of the scaled scores, saved for the backward pass
+        const float* rsl = red + 256 + hd * 128;
+        const float l = rsl[lane] + rsl[32 + lane] + rsl[64 + lane] + rsl[96 + lane];
+        const int t = qt * TQ + lane;
+        if (t < a.T) a.lse[(static_cast<long>(b) * a.H + hp * 2 + hd) * a.T + t] = l > 0.f ? col_max * a.scale + __logf(l) : INFINITY;
+      }
       // ---- epilogue: O^T rows of this quadrant belong to head (quad / 2); this warp takes 16 queries
       const int oh = quad >> 1;
       const int q0 = hd * 16;
@@ -319,6 +328,7 @@ int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st) {
   a.B = p->B; a.T = p->T; a.S = p->S; a.H = p->H;
   a.mask_S = p->mask_S > 0 ? p->mask_S : p->S;
   a.scale_log2e = p->scale * 1.4426950408889634f;
+  a.lse = p->lse; a.scale = p->scale;
   a.n_qt = (p->T + atc::TQ - 1) / atc::TQ;
   a.n_items = p->B * (p->H / 2) * a.n_qt;
   a.n_tiles = (p->S + atc::TKEYS - 1) / atc::TKEYS;

@@ -182,6 +182,14 @@ __global__ void __launch_bounds__(kWarps * 32) embed_kernel(tnt_embed_params p) 
   }
 }
 
+__device__ __forceinline__ void store4(float* p, float a, float b, float c, float d) {
+  *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+__device__ __forceinline__ void store4(bf16* p, float a, float b, float c, float d) {
+  *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(a, b), pack_bf16x2(c, d));
+}
+__device__ __forceinline__ bool dev_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
 // ------------------------------------------------------------------------------ weight-norm fold
 // w = g * v / ||v||_row  (linear.py:30-33); optional GLU pair interleave of the output rows.
 template <typename T>
@@ -191,16 +199,31 @@ __global__ void __launch_bounds__(kWarps * 32) wn_fold_kernel(const float* v, co
   const int row = blockIdx.x * kWarps + (threadIdx.x >> 5);
   if (row >= rows) return;
   const float* vr = v + static_cast<long>(row) * cols;
+  const bool vec = (cols & 3) == 0 && dev_aligned16(v) && dev_aligned16(out);
   float scale = 1.f;
   if (g) {
     float sq = 0.f;
-    for (int c = lane; c < cols; c += 32) sq = fmaf(vr[c], vr[c], sq);
+    if (vec) {
+      for (int c = lane * 4; c < cols; c += 128) {
+        const float4 a = *reinterpret_cast<const float4*>(vr + c);
+        sq = fmaf(a.x, a.x, fmaf(a.y, a.y, fmaf(a.z, a.z, fmaf(a.w, a.w, sq))));
+      }
+    } else {
+      for (int c = lane; c < cols; c += 32) sq = fmaf(vr[c], vr[c], sq);
+    }
     scale = g[row] / sqrtf(warp_sum(sq));
   }
   int orow = row;
   if (glu) orow = row < rows / 2 ? 2 * row : 2 * (row - rows / 2) + 1;
   T* o = out + static_cast<long>(orow) * cols;
-  for (int c = lane; c < cols; c += 32) o[c] = from_f<T>(vr[c] * scale);
+  if (vec) {
+    for (int c = lane * 4; c < cols; c += 128) {
+      const float4 a = *reinterpret_cast<const float4*>(vr + c);
+      store4(o + c, a.x * scale, a.y * scale, a.z * scale, a.w * scale);
+    }
+  } else {
+    for (int c = lane; c < cols; c += 32) o[c] = from_f<T>(vr[c] * scale);
+  }
 }
 
 __global__ void glu_bias_kernel(const float* b, float* out, int n) {

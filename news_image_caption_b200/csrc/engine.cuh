@@ -52,8 +52,10 @@ struct tnt_decoder {
   float* pos_table = nullptr;          // [max_positions, d]
   tnt::AdaSoftmax ada;
   void* scratch_dd = nullptr;          // [d, d] fp32 (finalize only)
+  void* emb_scratch = nullptr;             // largest band table in the engine dtype (finalize only)
   void* emb_proj[TNT_MAX_CLUSTERS] = {};   // band projections [d, dim_i] in the engine dtype (training backward)
   int emb_dim[TNT_MAX_CLUSTERS] = {};
+  std::vector<cudaEvent_t> stage_events;   // training: gradients of stage i are final (tnt_decoder_stream_wait_stage)
   std::map<std::string, float*> grads; // training: fp32 gradient buffer per state_dict key (tnt_decoder_set_grad)
   int article_idx = -1;
   // pipelined host scoring (tnt_decoder_score_host_submit / _wait): copy stream + per-slot events

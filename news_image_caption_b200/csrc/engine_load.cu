@@ -71,6 +71,15 @@ size_t plan(tnt_decoder* D, char* base) {
   }
   D->scratch_dd = a.take(d * d * 4);
   for (int i = 0; i < c.n_clusters; ++i) D->emb_proj[i] = a.take(d * d * E);
+  {
+    size_t max_band = 0;
+    int lo = 0;
+    for (int i = 0; i < c.n_clusters; ++i) {
+      max_band = std::max<size_t>(max_band, c.cutoffs[i] - lo);
+      lo = c.cutoffs[i];
+    }
+    D->emb_scratch = a.take(max_band * d * E);
+  }
   return a.off;
 }
 
@@ -266,14 +275,13 @@ extern "C" int tnt_decoder_finalize(tnt_decoder* D, tnt_stream stream) {
         }
         D->emb_dim[i] = dim_i;
         L.matrix(prj->data, D->emb_proj[i], d, dim_i);
-        scale_kernel<<<64, 256, 0, L.st>>>(prj->data, static_cast<float*>(D->scratch_dd), static_cast<long>(d) * dim_i,
-                                           sqrtf(static_cast<float>(d)));
-        count_launch();
+        // table_i (engine dtype copy) . proj_i^T * sqrt(d): tcgen05 GEMM for the bf16 engine, fp32 SIMT for parity mode
+        L.matrix(tab->data, D->emb_scratch, n_i, dim_i);
         tnt_linear_params lp = {};
-        lp.a = tab->data; lp.lda = dim_i; lp.w = D->scratch_dd; lp.ldw = dim_i;
+        lp.a = D->emb_scratch; lp.lda = dim_i; lp.w = D->emb_proj[i]; lp.ldw = dim_i;
         lp.c = static_cast<char*>(D->table) + static_cast<size_t>(lo) * d * D->esz(); lp.ldc = d;
-        lp.M = n_i; lp.N = d; lp.K = dim_i; lp.groups = 1;
-        lp.dtype_in = TNT_F32; lp.dtype_out = c.dtype; lp.epilogue = TNT_EPI_NONE;
+        lp.M = n_i; lp.N = d; lp.K = dim_i; lp.groups = 1; lp.alpha = sqrtf(static_cast<float>(d));
+        lp.dtype_in = c.dtype; lp.dtype_out = c.dtype; lp.epilogue = TNT_EPI_NONE;
         L.chk(tnt_linear_fwd(&lp, stream));
       }
       lo = c.cutoffs[i];

@@ -282,45 +282,35 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
 
 
 // ------------------------------------------------------------------------------ K/V projection parameters
-int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int s) {
+// of layer l, source s (k/v_proj_weight or in_proj_weight rows [d, 3d), in_proj_bias[d:], bias_k, bias_v): computed
+// right after the layer's backward so its gradients are final with the layer's stage.
+int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, int s) {
   tnt_decoder* D = c.D;
   const tnt_decoder_config& cf = D->cfg;
-  const int d = cf.d, Ls = cf.n_layers, kd = cf.source_dim[s], B = ctx->B, S = ctx->S[s];
-  const int ldkv = Ls * 2 * d;
+  const int d = cf.d, kd = cf.source_dim[s], B = ctx->B, S = ctx->S[s];
+  const int ldkv = cf.n_layers * 2 * d;
   const size_t E = D->esz();
-  // learned bias_k / bias_v row (key index S) of every layer
-  TNT_TRY(kv_extra_grad(w.dkv[s], ldkv, S, B, ldkv, w.vecs, c.dt, c.st));
-  for (int l = 0; l < Ls; ++l) {
-    const std::string at = "layers." + std::to_string(l) + ".context_attns." + cf.source_names[s] + ".";
-    float *gk = c.grad(at + "bias_k"), *gv = c.grad(at + "bias_v");
-    TNT_CHECK_ARG(gk && gv, "train: gradient buffer for '%sbias_k/v' missing", at.c_str());
-    TNT_CUDA(cudaMemcpyAsync(gk, w.vecs + static_cast<size_t>(l) * 2 * d, sizeof(float) * d, cudaMemcpyDeviceToDevice, c.st));
-    TNT_CUDA(cudaMemcpyAsync(gv, w.vecs + static_cast<size_t>(l) * 2 * d + d, sizeof(float) * d, cudaMemcpyDeviceToDevice, c.st));
-  }
-  // projection biases: column sums over the S*B memory rows
-  TNT_TRY(colsum(w.dkv[s], ldkv, S * B, ldkv, nullptr, w.vecs, c.dt, false, false, c.st));
-  // projection weights of all layers in one GEMM: dWkv [L*2d, kdim] = dKV^T . memory
+  const std::string at = "layers." + std::to_string(l) + ".context_attns." + cf.source_names[s] + ".";
+  const void* dkv = off(w.dkv[s], static_cast<size_t>(l) * 2 * d, E);     // columns [K | V] of this layer
+  float *gk = c.grad(at + "bias_k"), *gv = c.grad(at + "bias_v"), *gb = c.grad(at + "in_proj_bias");
+  TNT_CHECK_ARG(gk && gv && gb, "train: gradient buffer for '%sbias_k / bias_v / in_proj_bias' missing", at.c_str());
+  TNT_TRY(kv_extra_grad(dkv, ldkv, S, B, 2 * d, w.vecs, c.dt, c.st));      // the learned extra key row (index S)
+  TNT_CUDA(cudaMemcpyAsync(gk, w.vecs, sizeof(float) * d, cudaMemcpyDeviceToDevice, c.st));
+  TNT_CUDA(cudaMemcpyAsync(gv, w.vecs + d, sizeof(float) * d, cudaMemcpyDeviceToDevice, c.st));
+  TNT_TRY(colsum(dkv, ldkv, S * B, 2 * d, nullptr, gb + d, c.dt, false, false, c.st));
+  float* gi = c.grad(at + "in_proj_weight");
+  float* dst = gi ? gi + static_cast<size_t>(d) * d : w.dW;
   if (S * B > 0) {
-    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.dkv[s], ldkv, ctx->memory[s], kd, w.dW, kd, ldkv, kd, S * B, TNT_F32));
+    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, dkv, ldkv, ctx->memory[s], kd, dst, kd, 2 * d, kd, S * B, TNT_F32));
   } else {
-    TNT_CUDA(cudaMemsetAsync(w.dW, 0, sizeof(float) * ldkv * kd, c.st));
+    TNT_CUDA(cudaMemsetAsync(dst, 0, sizeof(float) * 2 * d * kd, c.st));
   }
-  for (int l = 0; l < Ls; ++l) {
-    const std::string at = "layers." + std::to_string(l) + ".context_attns." + cf.source_names[s] + ".";
-    const float* src = w.dW + static_cast<size_t>(l) * 2 * d * kd;
-    float* gb = c.grad(at + "in_proj_bias");
-    TNT_CHECK_ARG(gb, "train: gradient buffer for '%sin_proj_bias' missing", at.c_str());
-    TNT_CUDA(cudaMemcpyAsync(gb + d, w.vecs + static_cast<size_t>(l) * 2 * d, sizeof(float) * 2 * d, cudaMemcpyDeviceToDevice, c.st));
-    if (float* gi = c.grad(at + "in_proj_weight")) {
-      TNT_CUDA(cudaMemcpyAsync(gi + static_cast<size_t>(d) * d, src, sizeof(float) * 2 * d * kd, cudaMemcpyDeviceToDevice, c.st));
-    } else {
-      float *gk = c.grad(at + "k_proj_weight"), *gv = c.grad(at + "v_proj_weight");
-      TNT_CHECK_ARG(gk && gv, "train: gradient buffer for '%sk/v_proj_weight' missing", at.c_str());
-      TNT_CUDA(cudaMemcpyAsync(gk, src, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, c.st));
-      TNT_CUDA(cudaMemcpyAsync(gv, src + static_cast<size_t>(d) * kd, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, c.st));
-    }
+  if (!gi) {
+    float *gwk = c.grad(at + "k_proj_weight"), *gwv = c.grad(at + "v_proj_weight");
+    TNT_CHECK_ARG(gwk && gwv, "train: gradient buffer for '%sk/v_proj_weight' missing", at.c_str());
+    TNT_CUDA(cudaMemcpyAsync(gwk, w.dW, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, c.st));
+    TNT_CUDA(cudaMemcpyAsync(gwv, w.dW + static_cast<size_t>(d) * kd, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, c.st));
   }
-  (void)E;
   return TNT_OK;
 }
 
@@ -394,6 +384,11 @@ extern "C" int tnt_decoder_train_step(tnt_decoder* D, const int64_t* ids, const 
   }
   cudaStream_t st = as_stream(stream);
   Ctx c{D, st, cf.dtype};
+  while (static_cast<int>(D->stage_events.size()) < Ls + 2) {
+    cudaEvent_t e;
+    TNT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    D->stage_events.push_back(e);
+  }
   // ---------------- forward
   {
     FwdWs f0 = layer_ws(w, 0, ns);
@@ -423,11 +418,23 @@ extern "C" int tnt_decoder_train_step(tnt_decoder* D, const int64_t* ids, const 
                              d_out, w.loss_bwd, w.loss_bwd_bytes, st));
   TNT_TRY(permute_rows(w.dXbt, w.gA, B, T, d, cf.dtype, true, st));                    // B x T -> T x B rows
   // ---------------- backward: layers, K/V projections, embedding
+  TNT_CUDA(cudaEventRecord(D->stage_events[0], st));
   for (int l = Ls - 1; l >= 0; --l) {
     const void* xin = l == 0 ? w.emb : w.act[l - 1].Xout;
     TNT_TRY(layer_bwd(c, ctx, w, l, xin));
+    for (int s = 0; s < ns; ++s) TNT_TRY(kv_param_grads(c, ctx, w, l, s));
+    TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], st));
   }
-  for (int s = 0; s < ns; ++s) TNT_TRY(kv_param_grads(c, ctx, w, s));
   TNT_TRY(embed_bwd(c, ids, B, T, w, w.gA));
+  TNT_CUDA(cudaEventRecord(D->stage_events[Ls + 1], st));
+  return TNT_OK;
+}
+
+extern "C" int tnt_decoder_train_stages(const tnt_decoder* d) { return d ? d->cfg.n_layers + 2 : 0; }
+
+extern "C" int tnt_decoder_stream_wait_stage(tnt_decoder* d, int stage, tnt_stream stream) {
+  TNT_CHECK_ARG(d && stage >= 0 && stage < static_cast<int>(d->stage_events.size()),
+                "stream_wait_stage: no training step has been issued, or bad stage");
+  TNT_CUDA(cudaStreamWaitEvent(as_stream(stream), d->stage_events[stage], 0));
   return TNT_OK;
 }

@@ -1,0 +1,100 @@
+// Fused optimizer step over the flat fp32 parameter / gradient arenas: BertAdam as the
+// reference configures it (ttl/expt/nytimes/9_transformer_objects/config.yaml:126-136 -> AllenNLP `bert_adam`
+// = pytorch_pretrained_bert.BertAdam, un-vendored third party; published algorithm restated here):
+//   per PARAMETER TENSOR gradient clipping to max_grad_norm, m = b1 m + (1-b1) g, v = b2 v + (1-b2) g^2,
+//   update = m / (sqrt(v) + eps) + weight_decay * p  (no bias correction),  p -= lr_scheduled * update.
+// Replaces the roles of apex multi_tensor_l2norm / multi_tensor_scale / multi_tensor_adam
+// (ttl/libs/apex/csrc/multi_tensor_{l2norm_kernel,scale_kernel,adam}.cu) on this path.  HBM-bound:
+// 16 B read + 12 B written per parameter.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace tnt {
+namespace {
+
+constexpr int kChunk = 64;      // arena segments are padded to 64 elements; one segment id per chunk
+
+// sum of squares per segment (segment = one parameter tensor).  Every warp owns a CONTIGUOUS run of chunks and
+// flushes one atomicAdd per segment change, so a 150 M-element arena costs a few thousand atomics.
+__global__ void __launch_bounds__(256) seg_sqnorm_kernel(const float* g, long n_chunks, const int* seg_of_chunk, float* seg_sq) {
+  const int lane = threadIdx.x & 31;
+  const long warp = (blockIdx.x * 256L + threadIdx.x) >> 5;
+  const long nw = (gridDim.x * 256L) >> 5;
+  const long per = (n_chunks + nw - 1) / nw;
+  const long c0 = warp * per, c1 = min(n_chunks, c0 + per);
+  float acc = 0.f;
+  int cur = c0 < c1 ? seg_of_chunk[c0] : -1;
+  for (long c = c0; c < c1; ++c) {
+    const int sg = seg_of_chunk[c];
+    if (sg != cur) {
+      acc = warp_sum(acc);
+      if (lane == 0 && acc != 0.f) atomicAdd(seg_sq + cur, acc);
+      acc = 0.f;
+      cur = sg;
+    }
+    const float2 v = *reinterpret_cast<const float2*>(g + c * kChunk + lane * 2);
+    acc = fmaf(v.x, v.x, fmaf(v.y, v.y, acc));
+  }
+  if (cur >= 0) {
+    acc = warp_sum(acc);
+    if (lane == 0 && acc != 0.f) atomicAdd(seg_sq + cur, acc);
+  }
+}
+
+__global__ void __launch_bounds__(256) bert_adam_kernel(float* p, const float* g, float* m, float* v, long n_chunks,
+                                                        const int* seg_of_chunk, const float* seg_sq,
+                                                        const float* gscale_dev, float gscale_host, float max_norm,
+                                                        float lr, float b1, float b2, float eps, float wd) {
+  const float gs = gscale_host * (gscale_dev ? *gscale_dev : 1.f);
+  const long total4 = n_chunks * (kChunk / 4);
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < total4; i += gridDim.x * 256L) {
+    const long c = i / (kChunk / 4);
+    float coef = gs;
+    if (max_norm > 0.f && seg_sq) {
+      const float norm = sqrtf(seg_sq[seg_of_chunk[c]]) * gs;
+      const float clip = max_norm / (norm + 1e-6f);          // torch.nn.utils.clip_grad_norm_
+      if (clip < 1.f) coef *= clip;
+    }
+    const float4 gg = reinterpret_cast<const float4*>(g)[i];
+    float4 pp = reinterpret_cast<float4*>(p)[i], mm = reinterpret_cast<float4*>(m)[i], vv = reinterpret_cast<float4*>(v)[i];
+    float* pa = &pp.x; float* ma = &mm.x; float* va = &vv.x;
+    const float* ga = &gg.x;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float gr = ga[j] * coef;
+      ma[j] = b1 * ma[j] + (1.f - b1) * gr;
+      va[j] = b2 * va[j] + (1.f - b2) * gr * gr;
+      const float upd = ma[j] / (sqrtf(va[j]) + eps) + wd * pa[j];
+      pa[j] -= lr * upd;
+    }
+    reinterpret_cast<float4*>(p)[i] = pp;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    reinterpret_cast<float4*>(v)[i] = vv;
+  }
+}
+}  // namespace
+}  // namespace tnt
+
+extern "C" int tnt_bert_adam_step(const tnt_adam_params* a, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(a && a->params && a->grads && a->m && a->v, "bert_adam: null pointer");
+  TNT_CHECK_ARG(a->n % kChunk == 0, "bert_adam: arena length must be a multiple of 64");
+  TNT_CHECK_ARG(a->max_grad_norm <= 0.f || (a->seg_of_chunk && a->seg_sq && a->n_segments > 0),
+                "bert_adam: per-tensor clipping needs the segment table");
+  TNT_CHECK_ALIGN(aligned16(a->params) && aligned16(a->grads) && aligned16(a->m) && aligned16(a->v), "bert_adam: alignment");
+  if (a->n == 0) return TNT_OK;
+  cudaStream_t st = as_stream(stream);
+  const long n_chunks = a->n / kChunk;
+  const int grid = static_cast<int>(std::min<long>((a->n / 4 + 255) / 256, 16L * num_sms()));
+  if (a->max_grad_norm > 0.f) {
+    TNT_CUDA(cudaMemsetAsync(a->seg_sq, 0, sizeof(float) * a->n_segments, st));
+    seg_sqnorm_kernel<<<grid, 256, 0, st>>>(a->grads, n_chunks, a->seg_of_chunk, a->seg_sq);
+    TNT_LAUNCHED();
+  }
+  bert_adam_kernel<<<grid, 256, 0, st>>>(a->params, a->grads, a->m, a->v, n_chunks, a->seg_of_chunk, a->seg_sq,
+                                         a->grad_scale_dev, a->grad_scale != 0.f ? a->grad_scale : 1.f, a->max_grad_norm,
+                                         a->lr, a->beta1, a->beta2, a->eps, a->weight_decay);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}

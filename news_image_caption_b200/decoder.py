@@ -313,10 +313,22 @@ class DynamicConvDecoder(nn.Module):
                 mod = getattr(mod, q)
             mod._parameters[parts[-1]] = own[owner]
         named = [(k, p) for k, p in self.named_parameters() if 'token_embedder_position' not in k]
+        # arena order = the order in which the backward pass finishes gradients (tnt_decoder_train_stages):
+        # softmax-only parameters, layers last -> first, embedding bands (tied output rows) last
+        n_layers = len(self.kernels)
+
+        def stage_of(k):
+            if k.startswith('adaptive_softmax.'):
+                return 0
+            if k.startswith('layers.'):
+                return n_layers - int(k.split('.')[1])
+            return n_layers + 1
+        named.sort(key=lambda kp: stage_of(kp[0]))
         total = sum((p.numel() + 63) // 64 * 64 for _, p in named)
-        self.flat_params = torch.empty(total, dtype=torch.float32, device='cuda')
+        self.flat_params = torch.zeros(total, dtype=torch.float32, device='cuda')
         self.flat_grads = torch.zeros(total, dtype=torch.float32, device='cuda')
         self.param_slices = {}
+        self.stage_slices = [[None, None] for _ in range(n_layers + 2)]
         off = 0
         L = _lib.lib()
         with torch.no_grad():
@@ -328,7 +340,10 @@ class DynamicConvDecoder(nn.Module):
                 p.requires_grad_(True)
                 p.grad = self.flat_grads[off:off + n].view(p.shape)
                 self.param_slices[k] = (off, n)
+                st = self.stage_slices[stage_of(k)]
+                st[0] = off if st[0] is None else st[0]
                 off += (n + 63) // 64 * 64
+                st[1] = off
         self._dirty = True
         h = self._h()
         for k, p in named:

@@ -429,3 +429,29 @@ def v2_translate(memory, sd: SD, h: int, max_len: int, bos: int = 0):
         z = F.linear(out[:, -1], sd['generator.proj.weight'], sd['generator.proj.bias'])
         ys = torch.cat([ys, F.log_softmax(z, -1).argmax(-1, keepdim=True)], 1)
     return ys
+
+
+# ----------------------------------------------------------------------------- optimizer
+def warmup_linear(x: float, warmup: float) -> float:
+    return x / warmup if x < warmup else max((x - 1.0) / (warmup - 1.0), 0.0)
+
+
+def bert_adam_step(params: SD, grads: SD, state: dict, lr: float, b1: float = 0.9, b2: float = 0.98,
+                   e: float = 1e-6, weight_decay: float = 1e-5, max_grad_norm: float = 0.1):
+    """One BertAdam update, the optimizer the reference configures (config.yaml:126-136, AllenNLP `bert_adam`
+    = pytorch_pretrained_bert.optimization.BertAdam 0.6.x -- un-vendored third party; published algorithm):
+    per-parameter clip_grad_norm_, no bias correction, L2 weight decay added to the update.  In place."""
+    for k, p in params.items():
+        g = grads[k].clone()
+        if max_grad_norm > 0:
+            coef = max_grad_norm / (g.norm() + 1e-6)
+            if coef < 1:
+                g = g * coef
+        m = state.setdefault(('m', k), torch.zeros_like(p))
+        v = state.setdefault(('v', k), torch.zeros_like(p))
+        m.mul_(b1).add_(g, alpha=1 - b1)
+        v.mul_(b2).addcmul_(g, g, value=1 - b2)
+        upd = m / (v.sqrt() + e)
+        if weight_decay > 0:
+            upd = upd + weight_decay * p
+        p.sub_(lr * upd)

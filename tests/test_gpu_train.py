@@ -111,3 +111,53 @@ def test_train_step_gradients(name, dtype):
         worst.append((err(p.grad, go), k))
     worst.sort(reverse=True)
     assert worst[0][0] < gtol, '\n'.join('%.3e %s' % w for w in worst[:12])
+
+
+def test_gradients_are_additive_over_batch_shards():
+    """Data-parallel invariant: summed gradients of two half-batches == gradients of the whole
+    batch (each rank back-propagates the un-normalised sum loss), and the losses / token counts add up."""
+    f = torch.load(os.path.join(G, 'tell4_small.pt'), weights_only=False)
+    dec = make_decoder(f['config'], f['state_dict'], torch.float32).enable_training()
+    prev, tgt = f['prev'].cuda(), f['target'].cuda()
+    ctx = {k: v.cuda() for k, v in f['contexts'].items()}
+    B = prev.shape[0]
+    full = dec.train_step(prev, tgt, ctx).clone()
+    g_full = dec.flat_grads.clone()
+    acc, outs = torch.zeros_like(g_full), torch.zeros_like(full)
+    for sl in (slice(0, B // 2), slice(B // 2, B)):
+        c = {k: (v[sl] if k.endswith('_mask') else v[:, sl]).contiguous() for k, v in ctx.items()}
+        outs += dec.train_step(prev[sl].contiguous(), tgt[sl].contiguous(), c)
+        acc += dec.flat_grads
+    assert outs[1].item() == full[1].item()
+    assert abs(outs[0].item() - full[0].item()) < 1e-5 * abs(full[0].item())
+    assert rel_err(acc, g_full) < 1e-4
+
+
+def test_trainer_two_steps_match_oracle_bert_adam():
+    """Trainer.step (engine backward + fused BertAdam with per-tensor clipping and the 1/(n_tokens ln 2) loss
+    normalisation) against the oracle: autograd through the restated decoder + the restated BertAdam."""
+    import math
+    from news_image_caption_b200.trainer import Trainer
+    f = torch.load(os.path.join(G, 'tell2_small.pt'), weights_only=False)
+    cfg = f['config']
+    dec = make_decoder(cfg, f['state_dict'], torch.float32)
+    tr = Trainer(dec, lr=1e-2, max_grad_norm=0.1, weight_decay=1e-3, t_total=10, warmup=0.2)
+    ctx = {k: v.cuda() for k, v in f['contexts'].items()}
+    ties = O.tied_output_keys(len(cfg['cutoffs']))
+    sd = O.leaf_state_dict(f['state_dict'], ties)
+    own = dict(dec.named_parameters())
+    trainable = {k: v for k, v in sd.items() if k in own and k not in ties and 'token_embedder_position' not in k}
+    state = {}
+    for step in range(2):
+        out = tr.step(f['prev'].cuda(), f['target'].cuda(), ctx)
+        X, _ = O.decoder_forward(f['prev'], f['contexts'], sd, cfg['heads'], cfg['cutoffs'], cfg['sources'])
+        loss, n = O.adaptive_nll(X, f['target'], sd, cfg['cutoffs'])
+        assert abs(out[0].item() - loss.item()) < 1e-4 * abs(loss.item()) and int(out[1].item()) == n
+        grads = dict(zip(trainable, torch.autograd.grad(loss / n / math.log(2.0), list(trainable.values()))))
+        with torch.no_grad():
+            O.bert_adam_step(trainable, grads, state, lr=1e-2 * O.warmup_linear(step / 10, 0.2), weight_decay=1e-3)
+    torch.cuda.synchronize()
+    worst = max((rel_err(own[k], v.detach()), k) for k, v in trainable.items())
+    # parameters whose true gradient is ~0 (key-projection biases: softmax is shift invariant) get Adam-normalised
+    # rounding noise, hence the looser bound
+    assert worst[0] < 1e-3, worst
