@@ -238,6 +238,9 @@ int launch(const BwdArgs& a, size_t smem, cudaStream_t st) {
 }  // namespace
 
 int xattn_check(const tnt_xattn_params* p);
+bool xattn_bwd_tc_supported(const XattnBwd* p);
+int xattn_bwd_tc(const XattnBwd* p, cudaStream_t st);
+static bool g_force_simt_attn_bwd = false;
 
 int xattn_bwd(const XattnBwd* p, cudaStream_t st) {
   TNT_CHECK_ARG(p && p->dout && p->dq && p->dk && p->dv, "xattn_bwd: null pointer");
@@ -245,6 +248,7 @@ int xattn_bwd(const XattnBwd* p, cudaStream_t st) {
   TNT_CHECK_ARG(p->f.n_extra == 0, "xattn_bwd: materialise the bias_k / zero rows in k, v (n_extra must be 0)");
   TNT_CHECK_ARG(p->scratch != nullptr, "xattn_bwd: fp32 scratch [B,H,T,D] missing");
   if (p->f.T == 0 || p->f.B == 0) return TNT_OK;
+  if (!g_force_simt_attn_bwd && xattn_bwd_tc_supported(p)) return xattn_bwd_tc(p, st);
   BwdArgs a;
   a.f = p->f;
   a.scratch = p->scratch;
@@ -257,6 +261,8 @@ int xattn_bwd(const XattnBwd* p, cudaStream_t st) {
 }
 
 }  // namespace tnt
+
+extern "C" void tnt_debug_force_simt_attention_bwd(int on) { tnt::g_force_simt_attn_bwd = on != 0; }
 
 extern "C" size_t tnt_xattn_bwd_scratch_bytes(int B, int T, int H, int D) {
   return sizeof(float) * static_cast<size_t>(B) * T * H * D;

@@ -81,6 +81,7 @@ struct FwdWs {
   void *X0, *X1, *h, *logits, *cbuf, *ybuf, *Q, *AO, *CAT, *F;
   void *ybuf2, *CATln;     // inference: aliases of ybuf / CAT; training keeps the pre-LayerNorm tensors
   void* kv[TNT_MAX_SOURCES];
+  float* lse[TNT_MAX_SOURCES];   // training: attention log-sum-exp [B, H, T] per source (NULL: not saved)
   size_t total;
 };
 FwdWs carve_fwd(const tnt_decoder* d, int B, int T, const int* S, void* ws, bool with_kv);

@@ -54,7 +54,7 @@ FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool
     off += al256(bytes);
     return p;
   };
-  FwdWs w;
+  FwdWs w = {};
   w.X0 = take(N * d * E); w.X1 = take(N * d * E); w.h = take(N * d * E);
   w.logits = take(N * D->max_ld_logits() * E);
   w.cbuf = take(N * d * E); w.ybuf = take(N * d * E);
@@ -133,6 +133,7 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     ap.mask = ctx->pad_mask[s]; ap.m_stride_b = ctx->S[s]; ap.m_stride_t = 0;
     ap.mask_mode = (ctx->pad_mask[s] && ctx->S[s] > 0) ? TNT_MASK_KEY_PADDING : TNT_MASK_NONE;
     ap.weights = (attn_out && s == D->article_idx) ? attn_out : nullptr;
+    ap.lse = w.lse[s];
     // the K/V buffer carries the 2 extra rows (project_kv), so they are plain keys the mask does not cover
     ap.B = B; ap.T = T; ap.S = ctx->S[s] + 2; ap.H = H; ap.D = d / H; ap.n_extra = 0;
     ap.mask_S = ctx->S[s];

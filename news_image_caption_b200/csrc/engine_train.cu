@@ -21,6 +21,7 @@ inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
 
 struct LayerAct {
   void *h, *logits, *cbuf, *yc, *X1, *Q, *AO, *CATpre, *CATln, *X0, *F, *yf, *Xout;
+  float* lse[TNT_MAX_SOURCES];
 };
 
 struct TrainWs {
@@ -61,6 +62,8 @@ TrainWs carve_train(const tnt_decoder* D, int B, int T, const int* S, void* ws) 
     a.yc = take(N * d * E); a.X1 = take(N * d * E); a.Q = take(N * ns * d * E); a.AO = take(N * ns * d * E);
     a.CATpre = take(N * ns * d * E); a.CATln = take(N * ns * d * E); a.X0 = take(N * d * E);
     a.F = take(N * c.ffn * E); a.yf = take(N * d * E); a.Xout = take(N * d * E);
+    for (size_t s = 0; s < TNT_MAX_SOURCES; ++s)
+      a.lse[s] = s < ns ? static_cast<float*>(take(N * c.heads * sizeof(float))) : nullptr;
   }
   size_t max_kdim = d;
   for (size_t s = 0; s < ns; ++s) {
@@ -162,7 +165,10 @@ FwdWs layer_ws(const TrainWs& w, int l, int ns) {
   const LayerAct& a = w.act[l];
   f.X0 = a.X0; f.X1 = a.X1; f.h = a.h; f.logits = a.logits; f.cbuf = a.cbuf; f.ybuf = a.yc; f.ybuf2 = a.yf;
   f.Q = a.Q; f.AO = a.AO; f.CAT = a.CATpre; f.CATln = a.CATln; f.F = a.F;
-  for (int s = 0; s < ns; ++s) f.kv[s] = w.kv[s];
+  for (int s = 0; s < ns; ++s) {
+    f.kv[s] = w.kv[s];
+    f.lse[s] = a.lse[s];
+  }
   return f;
 }
 
@@ -187,6 +193,7 @@ tnt_xattn_params attn_params(const tnt_decoder* D, const tnt_contexts* ctx, cons
   ap.mask_S = ctx->S[s];
   ap.scale = 1.0f / sqrtf(static_cast<float>(d / c.heads));
   ap.dtype = c.dtype;
+  ap.lse = a.lse[s];
   return ap;
 }
 

@@ -143,7 +143,8 @@ def layernorm_bwd(x, dy, gamma, eps=1e-5):
     return dx, dg, db
 
 
-def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=None, need_weights=False, mask_S=0):
+def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=None, need_weights=False, mask_S=0,
+          lse=None):
     """q [T,B,E], k/v [S,B,E] (projected) -> out [T,B,E] (+ head-averaged weights [B,T,S+n_extra]).
     pad_mask [B,S] bool True=pad (tell);  v2_mask [B,1|T,S] 'visible' mask (final*), 0 -> -1e9."""
     q, k, v = _cuda(q).contiguous(), k.contiguous(), v.contiguous()
@@ -176,12 +177,14 @@ def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=No
     if need_weights:
         w = torch.empty(B, T, S + n_extra, dtype=torch.float32, device=q.device)
         p.weights = w.data_ptr()
+    if lse is not None:
+        p.lse = lse.data_ptr()
     p.B, p.T, p.S, p.H, p.D, p.n_extra, p.scale, p.dtype = B, T, S, H, E // H, n_extra, scale, _code(q)
     _lib.check(_lib.lib().tnt_xattn_fwd(C.byref(p), _st()), 'tnt_xattn_fwd')
     return out, w
 
 
-def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=0):
+def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=0, lse=None):
     """Backward of `xattn` (n_extra = 0: extra rows are ordinary k / v rows).  Returns (dq, dk, dv)."""
     q, k, v, out, dout = [_cuda(t).contiguous() for t in (q, k, v, out, dout)]
     T, B, E = q.shape
@@ -205,6 +208,8 @@ def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=
         p.mask, p.m_stride_b, p.mask_mode = m.data_ptr(), m.shape[1] * S, MASK_V2
         p.m_stride_t = S if m.shape[1] > 1 else 0
     p.B, p.T, p.S, p.H, p.D, p.n_extra, p.scale, p.dtype = B, T, S, H, E // H, 0, scale, _code(q)
+    if lse is not None:
+        p.lse = lse.data_ptr()
     L = _lib.lib()
     scr = torch.empty(L.tnt_xattn_bwd_scratch_bytes(B, T, H, E // H) + 256, dtype=torch.uint8, device=q.device)
     bp.dout, bp.dq, bp.dk, bp.dv = dout.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr()

@@ -65,6 +65,43 @@ def test_xattn_backward(ops, T, S, H, D, mode, dtype):
     assert rel_err(dq, gq) < tol and rel_err(dk, gk) < tol and rel_err(dv, gv) < tol
 
 
+@pytest.mark.parametrize('T,S,B,H', [(32, 514, 3, 4), (7, 130, 2, 2), (40, 51, 5, 16), (64, 1000, 2, 2)])
+def test_xattn_backward_tcgen05(ops, T, S, B, H):
+    """The tcgen05 / TMEM backward kernel (bf16, D = 64, T <= 64, lse saved by the forward) against fp64
+    autograd and against the library's own SIMT backward on identical inputs."""
+    from news_image_caption_b200 import _lib
+    g = torch.Generator().manual_seed(T * 7 + S)
+    D, E = 64, H * 64
+    q = torch.randn(T, B, E, generator=g).bfloat16()
+    k = torch.randn(S, B, E, generator=g).bfloat16()
+    v = torch.randn(S, B, E, generator=g).bfloat16()
+    do = torch.randn(T, B, E, generator=g).bfloat16()
+    scale = D ** -0.5
+    pad = torch.rand(B, S, generator=g) > 0.7
+    pad[:, -2:] = False
+    pad[0, :-2] = True
+    qd, kd, vd = [t.double().requires_grad_(True) for t in (q, k, v)]
+    s = torch.einsum('tbhd,sbhd->bhts', qd.view(T, B, H, D), kd.view(S, B, H, D)) * scale
+    s = s.masked_fill(pad[:, None, None, :], float('-inf'))
+    o = torch.einsum('bhts,sbhd->tbhd', torch.softmax(s, -1), vd.view(S, B, H, D)).reshape(T, B, E)
+    gq, gk, gv = torch.autograd.grad(o, [qd, kd, vd], do.double())
+    lse = torch.empty(B, H, T, dtype=torch.float32, device='cuda')
+    args = dict(pad_mask=pad.cuda(), mask_S=S - 2)
+    out, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, scale, lse=lse, **args)
+    assert rel_err(lse, torch.logsumexp(s, -1).detach()) < 1e-2
+    dq, dk, dv = ops.xattn_bwd(q.cuda(), k.cuda(), v.cuda(), out, do.cuda(), H, scale, lse=lse, **args)
+    torch.cuda.synchronize()
+    for a_, b_ in ((dq, gq), (dk, gk), (dv, gv)):
+        assert rel_err(a_, b_) < 3e-2
+    _lib.lib().tnt_debug_force_simt_attention_bwd(1)
+    try:
+        sq, sk, sv = ops.xattn_bwd(q.cuda(), k.cuda(), v.cuda(), out, do.cuda(), H, scale, **args)
+    finally:
+        _lib.lib().tnt_debug_force_simt_attention_bwd(0)
+    for a_, b_ in ((dq, sq), (dk, sk), (dv, sv)):
+        assert rel_err(a_, b_) < 2e-2
+
+
 def make_decoder(cfg, sd, dtype):
     from news_image_caption_b200 import DynamicConvDecoder, build
     build.build()
@@ -161,3 +198,28 @@ def test_trainer_two_steps_match_oracle_bert_adam():
     # parameters whose true gradient is ~0 (key-projection biases: softmax is shift invariant) get Adam-normalised
     # rounding noise, hence the looser bound
     assert worst[0] < 1e-3, worst
+
+
+def test_train_step_full_width_bf16():
+    """BASELINE.json model width (d=1024, 16 heads of 64, ffn 4096, V=50265, cutoffs 5000/20000), 2 layers:
+    the tcgen05 paths (NT / NN / TN GEMMs, attention forward + backward, softmax-gradient epilogue) against
+    fp32 autograd through the oracle on the CPU."""
+    from news_image_caption_b200 import DynamicConvDecoder, build
+    from news_image_caption_b200.decoder import random_state_dict
+    build.build()
+    kernels, cut = (3, 31), (5000, 20000, 50265)
+    sd0 = random_state_dict(kernels=kernels, seed=3)
+    prev, tgt, ctx = synth.make_batch(3, 12, 50265, ('image', 'article'), seed=21, S_img=49, S_art=140)
+    sd = O.leaf_state_dict(sd0, O.tied_output_keys(3))
+    X, _ = O.decoder_forward(prev, ctx, sd, 16, list(cut), ('image', 'article'))
+    loss, n = O.adaptive_nll(X, tgt, sd, list(cut))
+    loss.backward()
+    dec = DynamicConvDecoder(decoder_kernel_size_list=kernels, dtype=torch.bfloat16)
+    dec.load_reference_state_dict(sd0)
+    dec.enable_training()
+    out = dec.train_step(prev.cuda(), tgt.cuda(), {k: v.cuda() for k, v in ctx.items()})
+    torch.cuda.synchronize()
+    assert int(out[1].item()) == n and abs(out[0].item() - loss.item()) < 2e-2 * abs(loss.item())
+    worst = sorted(((l2_err(p.grad, sd[k].grad), k) for k, p in dec.named_parameters()
+                    if 'token_embedder_position' not in k), reverse=True)
+    assert worst[0][0] < 1e-1, '\n'.join('%.3e %s' % w for w in worst[:10])
