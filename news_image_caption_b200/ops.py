@@ -115,15 +115,19 @@ def dynconv_step(x, logits, ring, pos, H, K):
     return y
 
 
-def layernorm(x, gamma, beta, eps=1e-5, variant=0):
+def layernorm(x, gamma, beta, eps=1e-5, variant=0, transpose_tb=None):
+    """LayerNorm over the last dim.  variant 1 = final*/transformer_v2.py LayerNorm (unbiased std, eps outside).
+    transpose_tb=(T, B): x rows are in t*B+b order and the output is written as [B, T, C]."""
     x = _cuda(x).contiguous()
     Cc = x.shape[-1]
-    y = torch.empty_like(x)
+    y = torch.empty_like(x) if transpose_tb is None else torch.empty(transpose_tb[1], transpose_tb[0], Cc, dtype=x.dtype, device=x.device)
     p = _lib.LayernormParams()
     p.x, p.ldx, p.y, p.ldy = x.data_ptr(), Cc, y.data_ptr(), Cc
     gamma, beta = gamma.float().contiguous(), beta.float().contiguous()
     p.gamma, p.beta = gamma.data_ptr(), beta.data_ptr()
     p.rows, p.C, p.groups, p.variant, p.eps, p.dtype = x.numel() // Cc, Cc, 1, variant, eps, _code(x)
+    if transpose_tb is not None:
+        p.transpose_T, p.transpose_B = transpose_tb
     _lib.check(_lib.lib().tnt_layernorm_fwd(C.byref(p), _st()), 'tnt_layernorm_fwd')
     return y
 
@@ -216,6 +220,40 @@ def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=
     bp.scratch, bp.scratch_bytes = scr.data_ptr(), scr.numel()
     _lib.check(L.tnt_xattn_bwd(C.byref(bp), _st()), 'tnt_xattn_bwd')
     return dq, dk, dv
+
+
+def embed(ids, table, pos_table, pad_idx, dtype):
+    """ids [B,T] -> [T,B,d] = table[ids] + pos_table[id == pad_idx ? pad_idx : t + pad_idx + 1]  (tnt_embed_fwd)."""
+    ids = _cuda(ids).to(torch.long).contiguous()
+    B, T = ids.shape
+    d = table.shape[1]
+    out = torch.empty(T, B, d, dtype=dtype, device=ids.device)
+    p = _lib.EmbedParams()
+    p.ids, p.table, p.pos_table, p.out, p.ldo = ids.data_ptr(), table.data_ptr(), pos_table.data_ptr(), out.data_ptr(), d
+    p.B, p.T, p.d, p.n_pos, p.pad_idx, p.dtype = B, T, d, pos_table.shape[0], pad_idx, _code(out)
+    _lib.check(_lib.lib().tnt_embed_fwd(C.byref(p), _st()), 'tnt_embed_fwd')
+    return out
+
+
+def xattn_strided(q, q_tb, k, k_sb, v, v_sb, B, T, S, H, D, scale, v2_mask=None):
+    """Attention over tensors addressed by explicit (time, batch) element strides: q_tb = (stride_t, stride_b) etc.
+    Output [T, B, H*D] (t*B+b rows).  v2_mask: bool, broadcastable to [B, T|1, S], 0 -> -1e9 (transformer_v2.py:217)."""
+    E = H * D
+    out = torch.empty(T, B, E, dtype=q.dtype, device=q.device)
+    p = _lib.XattnParams()
+    p.q, p.q_stride_t, p.q_stride_b = q.data_ptr(), q_tb[0], q_tb[1]
+    p.k, p.k_stride_s, p.k_stride_b = k.data_ptr(), k_sb[0], k_sb[1]
+    p.v, p.v_stride_s, p.v_stride_b = v.data_ptr(), v_sb[0], v_sb[1]
+    p.out, p.o_stride_t, p.o_stride_b = out.data_ptr(), B * E, E
+    p.mask_mode = MASK_NONE
+    m = None
+    if v2_mask is not None:
+        m = v2_mask.to(torch.bool).expand(B, v2_mask.shape[-2], S).contiguous()
+        p.mask, p.m_stride_b, p.mask_mode = m.data_ptr(), m.shape[1] * S, MASK_V2
+        p.m_stride_t = S if m.shape[1] > 1 else 0
+    p.B, p.T, p.S, p.H, p.D, p.n_extra, p.scale, p.dtype = B, T, S, H, D, 0, scale, _code(q)
+    _lib.check(_lib.lib().tnt_xattn_fwd(C.byref(p), _st()), 'tnt_xattn_fwd')
+    return out
 
 
 def lse(x, w, bias=None, target=None):
