@@ -4,5 +4,6 @@ host-side mirror of the reference's decoder / loss module interface.  No CPU fal
 from . import _lib  # noqa: F401
 from ._lib import TntError, lib, require_device  # noqa: F401
 from .decoder import AdaptiveLoss, DynamicConvDecoder  # noqa: F401
+from . import modules, transformer_v2  # noqa: F401  (module-level mirrors; nothing runs at import)
 
 __all__ = ['DynamicConvDecoder', 'AdaptiveLoss', 'lib', 'require_device', 'TntError']
