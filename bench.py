@@ -21,6 +21,15 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
 B_PER_GPU, T, S_IMG, S_ART, VOCAB = 64, 32, 49, 512, 50265
+SOURCES = ('image', 'article')
+# --workload: fwd = BASELINE configs[1] (default, the driver-run line); train = configs[2]; fwd4 = configs[3]
+# (NYTimes800k 4-source, B=128); gen = configs[4] (greedy generation, B=256, 32 steps)
+WORKLOADS = {
+    'fwd': dict(B=64, sources=('image', 'article'), tag='2src', what='fwd+adaptive-loss'),
+    'train': dict(B=64, sources=('image', 'article'), tag='2src', what='TRAIN fwd+bwd+grad-allreduce+BertAdam'),
+    'fwd4': dict(B=128, sources=('image', 'article', 'faces', 'obj'), tag='4src', what='fwd+adaptive-loss'),
+    'gen': dict(B=256, sources=('image', 'article'), tag='2src', what='GREEDY generation 32 steps (incremental DynamicConv ring + cached K/V)'),
+}
 # dram bytes (read + write) of one article K/V GEMM launch from the ncu --set full capture in profiles/ (None until captured)
 TRAFFIC_KV_GEMM = None
 WORKLOAD = 'tell-decoder-2src L4 d1024 H16 K3/7/15/31 V50265 fwd+adaptive-loss B64/gpu T32 S49+512'
@@ -78,7 +87,7 @@ class ClockSampler(threading.Thread):
 
 def make_inputs(seed):
     from oracle import synth          # pure torch input generator shared with the tests (no reference code)
-    return synth.make_batch(B_PER_GPU, T, VOCAB, ('image', 'article'), seed=seed, S_img=S_IMG, S_art=S_ART)
+    return synth.make_batch(B_PER_GPU, T, VOCAB, SOURCES, seed=seed, S_img=S_IMG, S_art=S_ART)
 
 
 def cpu_baseline_run(sd, cfg, n_iters, B):
@@ -86,7 +95,7 @@ def cpu_baseline_run(sd, cfg, n_iters, B):
     AdaptiveLoss at B captions.  Returns (tokens/s, seconds per iteration list)."""
     from oracle import restate as O
     from oracle import synth
-    prev, tgt, ctx = synth.make_batch(B, T, VOCAB, ('image', 'article'), seed=4321, S_img=S_IMG, S_art=S_ART)
+    prev, tgt, ctx = synth.make_batch(B, T, VOCAB, SOURCES, seed=4321, S_img=S_IMG, S_art=S_ART)
     ntok = int((tgt != 1).sum())
     times = []
     with torch.no_grad():
@@ -146,9 +155,14 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
-    ap.add_argument('--workload', default='fwd', choices=['fwd', 'train'],
-                    help='fwd = BASELINE configs[1] (the default, driver-run line); train = configs[2] (fwd+bwd+allreduce+BertAdam)')
+    ap.add_argument('--workload', default='fwd', choices=sorted(WORKLOADS),
+                    help='fwd = BASELINE configs[1] (the default, driver-run line); train = configs[2]; fwd4 = configs[3]; gen = configs[4]')
     args = ap.parse_args()
+    global B_PER_GPU, SOURCES, WORKLOAD
+    wl = WORKLOADS[args.workload]
+    B_PER_GPU, SOURCES = wl['B'], wl['sources']
+    WORKLOAD = 'tell-decoder-%s L4 d1024 H16 K3/7/15/31 V50265 %s B%d/gpu T32 S%s' % (
+        wl['tag'], wl['what'], B_PER_GPU, '49+512' if len(SOURCES) == 2 else '49+512+4+64')
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
     local = int(os.environ.get('LOCAL_RANK', 0))
@@ -170,8 +184,8 @@ def main():
     _lib.require_device()
     L = _lib.lib()
 
-    sd = random_state_dict(seed=0)
-    dec = DynamicConvDecoder(dtype=torch.bfloat16)
+    sd = random_state_dict(seed=0, sources=SOURCES)
+    dec = DynamicConvDecoder(sources=SOURCES, dtype=torch.bfloat16)
     dec.load_reference_state_dict(sd)
     dec.prepare()
     prev, tgt, ctx = make_inputs(1234 + rank)                     # batch shard of this rank (weak scaling)
@@ -189,9 +203,19 @@ def main():
         from news_image_caption_b200.trainer import Trainer
         trainer = Trainer(dec, t_total=100000)
 
+    gen = args.workload == 'gen'
+    GEN_LEN = T
+    if gen:
+        ntok = B_PER_GPU * GEN_LEN                   # tokens produced per step (finished rows keep their slot)
+        seed_d, seed_h = prev_d[:, :1].contiguous(), pin(prev[:, :1])
+        h2d = seed_h.numel() * 8 + sum(v.numel() * v.element_size() for v in ctx_h.values())
+
     def step():
         if trainer is not None:
             return trainer.step(prev_d, tgt_d, ctx_d)
+        if gen:
+            lp, ids = dec.generate(seed_d, ctx_d, gen_len=GEN_LEN, trim=False)
+            return ids
         X, _ = dec(prev_d, ctx_d, need_attn=False)
         return dec.nll(X, tgt_d)
 
@@ -222,6 +246,8 @@ def main():
     import ctypes as C
     kv_ms, kv_n = C.c_double(0), C.c_int(0)
     L.tnt_prof_read(b'kv_proj.article', C.byref(kv_ms), C.byref(kv_n))
+    xs_ms, xs_n = C.c_double(0), C.c_int(0)
+    L.tnt_prof_read(b'xattn_step.article', C.byref(xs_ms), C.byref(xs_n))
     L.tnt_prof_reset()
     ms = torch.tensor([e0.elapsed_time(e1)], device='cuda')
     ntok_all = torch.tensor([float(ntok)], device='cuda')
@@ -234,7 +260,27 @@ def main():
     # ---- end to end: pinned host buffers -> C ABI (H2D + forward + loss + D2H of the loss), every step.
     # Two batches are in flight (submit step i+1, then wait for step i): the H2D copies of one batch overlap
     # the compute of the other; every step still copies all of its inputs from pinned host memory.
-    if trainer is not None:
+    d2h = 8
+    if gen:
+        ids_ref = out.cpu()
+        ids_pin = torch.empty(B_PER_GPU, GEN_LEN + 1, dtype=torch.long).pin_memory()
+        lp_pin = torch.empty(B_PER_GPU, GEN_LEN, dtype=torch.float32).pin_memory()
+        d2h = ids_pin.numel() * 8 + lp_pin.numel() * 4
+
+        def e2e_gen():
+            c = {k: v.cuda(non_blocking=True) for k, v in ctx_h.items()}
+            lp, ids = dec.generate(seed_h.cuda(non_blocking=True), c, gen_len=GEN_LEN, trim=False)
+            ids_pin.copy_(ids, non_blocking=True)
+            lp_pin.copy_(lp, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        for _ in range(2):
+            e2e_gen()
+        sync_all()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_gen()
+        assert torch.equal(ids_pin, ids_ref), 'host-buffer generation differs from the device-resident run'
+    elif trainer is not None:
         def e2e_step():
             c = {k: v.cuda(non_blocking=True) for k, v in ctx_h.items()}
             o = trainer.step(prev_h.cuda(non_blocking=True), tgt_h.cuda(non_blocking=True), c)
@@ -261,7 +307,7 @@ def main():
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = ntok_all.item() * args.steps / e2e_s.item()
-    assert trainer is not None or (abs(l_h - loss_check[0].item()) < 1e-3 * abs(l_h) and int(n_h) == ntok), (l_h, loss_check, n_h, ntok)
+    assert trainer is not None or gen or (abs(l_h - loss_check[0].item()) < 1e-3 * abs(l_h) and int(n_h) == ntok), (l_h, loss_check, n_h, ntok)
 
     if rank != 0:
         if world > 1:
@@ -282,24 +328,52 @@ def main():
                 'shape': [M, N, K], 'ms_per_launch': gemm_ms, 'launches_timed': kv_n.value,
                 'share_of_step': gemm_ms / (ms_total / args.steps)}
 
+    if gen:
+        # dominant kernel of a decoding step: cross-attention over the cached article K/V (1 query per head):
+        # algorithmic bytes = K and V rows of this layer for every caption, (S+2) * 2 * d * 2 B, + q/out
+        byts = B_PER_GPU * ((S_ART + 2) * 2 * 1024 * 2 + 2 * 1024 * 2)
+        x_ms = xs_ms.value / max(xs_n.value, 1)
+        ach = byts / (x_ms * 1e-3) / 1e9 if x_ms > 0 else 0.0
+        roofline = {'bound': 'hbm', 'kernel': 'decode-step cross-attention over the cached article K/V (one layer)',
+                    'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': None,
+                    'peak_source': which + ' hbm_gbs', 'bytes_per_launch': byts, 'ms_per_launch': x_ms,
+                    'launches_timed': xs_n.value, 'note': 'timed on the eager step 0 of every generate call (steps 1.. replay a CUDA graph)',
+                    'kv_proj_gemm_tflops': achieved, 'kv_proj_ms': gemm_ms}
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and gen:
+        cores = len(os.sched_getaffinity(0))
+        torch.set_num_threads(cores)
+        from oracle import restate as O
+        from oracle import synth
+        Bs, Ls = 2, 8
+        p2, _, c2 = synth.make_batch(Bs, T, VOCAB, SOURCES, seed=4321, S_img=S_IMG, S_art=S_ART)
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            O.greedy_generate(p2[:, :1], c2, sd, 16, [5000, 20000, VOCAB], list(SOURCES), gen_len=Ls)
+        dt = time.perf_counter() - t0
+        cpu = {'value': Bs / (dt * GEN_LEN / Ls), 'unit': 'captions/s', 'cores': cores, 'kind': 'port',
+               'sample': 'oracle port greedy loop (reference _generate restated), fp32, B=%d, %d of %d steps timed (%.1f s), scaled linearly to %d steps' % (Bs, Ls, GEN_LEN, dt, GEN_LEN)}
+    elif not args.no_cpu_baseline:
         cores = len(os.sched_getaffinity(0))
         torch.set_num_threads(cores)
         cfg = dict(heads=16, cutoffs=[5000, 20000, VOCAB], sources=['image', 'article'])
+        cfg['sources'] = list(SOURCES)
         v, med, nt = cpu_baseline_run(sd, cfg, 3, 4)
         cpu = {'value': v, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port',
                'sample': 'oracle port (restated reference modules), fp32, B=4 T=32 fwd+loss, median of 3 (%.2f s/iter)' % med}
 
+    caps = B_PER_GPU * world * args.steps / (ms_total * 1e-3)
+    caps_e2e = B_PER_GPU * world * args.steps / e2e_s.item()
     print(json.dumps({
-        'metric': 'decoder_tokens_per_sec', 'value': value, 'unit': 'tokens/s', 'n_gpus': world, 'steps': args.steps,
+        'metric': 'captions_per_sec' if gen else 'decoder_tokens_per_sec', 'value': caps if gen else value,
+        'unit': 'captions/s' if gen else 'tokens/s', 'n_gpus': world, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': ms_total / args.steps, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
-        'config': {'workload': WORKLOAD if trainer is None else WORKLOAD.replace('fwd+adaptive-loss', 'TRAIN fwd+bwd+grad-allreduce+BertAdam'), 'l2': 'per-step working set (K/V 0.5 GB + activations) exceeds the 126 MB L2',
+        'config': {'workload': WORKLOAD, 'l2': 'per-step working set (K/V 0.5 GB + activations) exceeds the 126 MB L2',
                    'non_pad_tokens_per_step_per_gpu': ntok},
-        'captions_per_sec': B_PER_GPU * world * args.steps / (ms_total * 1e-3),
-        'e2e': {'value': e2e_value, 'unit': 'tokens/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 8,
-                'captions_per_sec': B_PER_GPU * world * args.steps / e2e_s.item()},
+        'captions_per_sec': caps, 'decoder_tokens_per_sec': value,
+        'e2e': {'value': caps_e2e if gen else e2e_value, 'unit': 'captions/s' if gen else 'tokens/s',
+                'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h, 'captions_per_sec': caps_e2e},
         'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roofline, 'cpu_baseline': cpu}))
     if world > 1:
         dist.destroy_process_group()

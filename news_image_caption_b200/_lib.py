@@ -142,6 +142,7 @@ _SIGS = {
     'tnt_decoder_stream_wait_stage': (i32, [vp, i32, vp]),
     'tnt_bert_adam_step': (i32, [C.POINTER(AdamParams), vp]),
     'tnt_debug_force_simt_gemm': (None, [i32]),
+    'tnt_debug_gemm_cta_group': (None, [i32]),
     'tnt_debug_force_simt_attention': (None, [i32]),
     'tnt_debug_force_simt_attention_bwd': (None, [i32]),
 }

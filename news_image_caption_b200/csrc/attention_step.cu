@@ -1,0 +1,176 @@
+// Decoding-step cross attention (kernel group 5): ONE query per (caption, head) against the cached K/V of a
+// source -- the T == 1 case of MultiHeadAttention.forward during `_generate`
+//   ttl/tell/modules/attention/multi_head.py:376-486 (scores, key_padding_mask -> -inf, fp32 softmax, PV)
+//   ttl/tell/models/transformer_flattened.py:238-325 (the step loop that calls it once per layer and source).
+// The work is a pure HBM stream: every K and V row of the caption is read exactly once (2 * (S+2) * d * 2 B per
+// caption and layer) for ~4 FLOP per byte, so the kernel is built around coalesced 16-byte loads with many rows
+// in flight, not around tensor cores:
+//   CTA   = (caption b, group of 8 heads): the 8 heads' K (or V) values of one key are 1 KB contiguous in the
+//           cache [S, B, L*2d]; padded keys (key_padding_mask) are never fetched (exp(-inf) = 0 exactly).
+//   warp  = a strided subset of the keys; lane = (head = lane / 4, 16 of the 64 dims): scores by 2 shuffles,
+//           running (max, sum, acc[16]) per lane in fp32 (flash-decoding), kUnroll keys loaded before use.
+//   merge = the warps' partial (max, sum, acc) through shared memory; bf16 output, optional LSE.
+#include "common.cuh"
+
+namespace tnt {
+namespace {
+
+constexpr int kHeadsPerCta = 8;
+constexpr int kWarps = 4;
+constexpr int kUnroll = 4;
+constexpr int kMaxKeys = 2048;
+
+__device__ __forceinline__ void unpack16(const uint4& a, const uint4& b, float (&v)[16]) {
+  const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+__device__ __forceinline__ uint4 ldg_stream(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+__global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(tnt_xattn_params p) {
+  __shared__ float sm_m[kWarps][32], sm_l[kWarps][32];
+  __shared__ float sm_acc[kWarps][32][17];
+  __shared__ uint8_t sm_mask[kMaxKeys];
+  __shared__ uint16_t sm_live[kMaxKeys];
+  __shared__ int sm_nlive;
+  const int b = blockIdx.x, hg = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int h = hg * kHeadsPerCta + (lane >> 2), d0 = (lane & 3) * 16;
+  const bf16* qp = reinterpret_cast<const bf16*>(p.q) + static_cast<long>(b) * p.q_stride_b + h * 64 + d0;
+  const bf16* kp = reinterpret_cast<const bf16*>(p.k) + static_cast<long>(b) * p.k_stride_b + h * 64 + d0;
+  const bf16* vp = reinterpret_cast<const bf16*>(p.v) + static_cast<long>(b) * p.v_stride_b + h * 64 + d0;
+  const int S = p.S;
+  const int SM = p.mask_mode == TNT_MASK_KEY_PADDING ? (p.mask_S > 0 ? min(p.mask_S, S) : S) : 0;   // keys the mask covers
+  const uint8_t* mrow = p.mask + static_cast<long>(b) * p.m_stride_b;
+
+  float q[16];
+  {
+    const uint4 a = *reinterpret_cast<const uint4*>(qp), c = *reinterpret_cast<const uint4*>(qp + 8);
+    unpack16(a, c, q);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) q[i] *= p.scale * 1.4426950408889634f;     // scores in the log2 domain
+  }
+  float m = -INFINITY, l = 0.f, acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+
+  // live (un-padded) keys of this caption, compacted once per CTA: the mask bytes are fetched by all threads at
+  // once (one memory latency), warp 0 turns them into an index list with ballots
+  for (int i = threadIdx.x; i < S; i += kWarps * 32) sm_mask[i] = i < SM ? mrow[i] : uint8_t(0);
+  __syncthreads();
+  if (warp == 0) {
+    int cnt = 0;
+    for (int base = 0; base < S; base += 32) {
+      const int kx = base + lane;
+      const bool lv = kx < S && sm_mask[kx] == 0;
+      const unsigned bal = __ballot_sync(0xffffffffu, lv);
+      if (lv) sm_live[cnt + __popc(bal & ((1u << lane) - 1u))] = static_cast<uint16_t>(kx);
+      cnt += __popc(bal);
+    }
+    if (lane == 0) sm_nlive = cnt;
+  }
+  __syncthreads();
+  const int n_live = sm_nlive;
+
+  // warp w takes live keys w, w + kWarps, ...; the K and V rows of kUnroll keys are requested before any is consumed
+  for (int j0 = warp; j0 < n_live; j0 += kWarps * kUnroll) {
+    uint4 kr[kUnroll][2], vr[kUnroll][2];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int j = j0 + u * kWarps;
+      if (j < n_live) {
+        const long ky = sm_live[j];
+        const bf16* kk = kp + ky * p.k_stride_s;
+        const bf16* vv = vp + ky * p.v_stride_s;
+        kr[u][0] = ldg_stream(kk);
+        kr[u][1] = ldg_stream(kk + 8);
+        vr[u][0] = ldg_stream(vv);
+        vr[u][1] = ldg_stream(vv + 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      if (j0 + u * kWarps < n_live) {                    // warp-uniform
+        float kf[16];
+        unpack16(kr[u][0], kr[u][1], kf);
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) s = fmaf(q[i], kf[i], s);
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        const float mn = fmaxf(m, s);
+        const float corr = exp2f(m - mn), pe = exp2f(s - mn);
+        l = l * corr + pe;
+        m = mn;
+        float vf[16];
+        unpack16(vr[u][0], vr[u][1], vf);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc[i] = fmaf(pe, vf[i], acc[i] * corr);
+      }
+    }
+  }
+
+  sm_m[warp][lane] = m;
+  sm_l[warp][lane] = l;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) sm_acc[warp][lane][i] = acc[i];
+  __syncthreads();
+  if (warp == 0) {
+    float M = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) M = fmaxf(M, sm_m[w][lane]);
+    float Ls = 0.f, o[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) o[i] = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      const float mw = sm_m[w][lane];
+      const float f = mw == -INFINITY ? 0.f : exp2f(mw - M);
+      Ls += sm_l[w][lane] * f;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) o[i] = fmaf(sm_acc[w][lane][i], f, o[i]);
+    }
+    const float inv = Ls > 0.f ? 1.f / Ls : 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) o[i] *= inv;
+    bf16* op = reinterpret_cast<bf16*>(p.out) + static_cast<long>(b) * p.o_stride_b + h * 64 + d0;
+    float t0[8], t1[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      t0[i] = o[i];
+      t1[i] = o[8 + i];
+    }
+    store8(op, t0);
+    store8(op + 8, t1);
+    if (p.lse && (lane & 3) == 0)                        // natural-log LSE of the scaled, masked scores
+      p.lse[static_cast<long>(b) * p.H + h] = Ls > 0.f ? (M + log2f(Ls)) * 0.6931471805599453f : INFINITY;
+  }
+}
+
+}  // namespace
+
+bool xattn_step_supported(const tnt_xattn_params* p) {
+  if (p->T != 1 || p->dtype != TNT_BF16 || p->D != 64 || (p->H % kHeadsPerCta) != 0 || p->n_extra != 0 || p->weights)
+    return false;
+  if (p->mask_mode != TNT_MASK_NONE && p->mask_mode != TNT_MASK_KEY_PADDING) return false;
+  const long strides = p->q_stride_b | p->k_stride_s | p->k_stride_b | p->v_stride_s | p->v_stride_b | p->o_stride_b;
+  return p->S >= 1 && p->S <= kMaxKeys && (strides % 8) == 0 && aligned16(p->q) && aligned16(p->k) && aligned16(p->v) && aligned16(p->out);
+}
+
+int xattn_fwd_step(const tnt_xattn_params* p, cudaStream_t st) {
+  dim3 grid(p->B, p->H / kHeadsPerCta);
+  xattn_step_kernel<<<grid, kWarps * 32, 0, st>>>(*p);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+}  // namespace tnt

@@ -31,6 +31,8 @@ static std::mutex g_prof_mu;
 bool prof_enabled() { return g_prof_on; }
 int prof_begin(const char* name, cudaStream_t st) {
   if (!g_prof_on) return -1;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) return -1;   // graph capture: no timing events
   std::lock_guard<std::mutex> lk(g_prof_mu);
   ProfRec r;
   r.name = name;

@@ -141,7 +141,14 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     ap.scale = 1.0f / sqrtf(static_cast<float>(d / H));
     ap.dtype = dt;
     TNT_TRY(xattn_check(&ap));
+    int pid = -1;
+    if (prof_enabled()) {
+      char pname[48];
+      snprintf(pname, sizeof(pname), T == 1 ? "xattn_step.%s" : "xattn.%s", c.source_names[s]);
+      pid = prof_begin(pname, st);
+    }
     TNT_TRY(xattn_fwd_dispatch(&ap, st));
+    prof_end(pid, st);
   }
   TNT_TRY(linear(w.AO, static_cast<long>(ns) * d, L.wo, d, L.bo, w.CAT, static_cast<long>(ns) * d, N, d, d, dt, EPI_RESIDUAL,
                  w.X1, d, st, ns, d, static_cast<long>(d) * d, d, 0, d));

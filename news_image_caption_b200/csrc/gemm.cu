@@ -22,13 +22,34 @@ constexpr int kAccStride = 256;
 constexpr int kMaxStages = 8;
 constexpr int kSmemBudget = 220 * 1024;
 
-template <int EPI, typename TOut>
+// tile index -> (m tile, n tile, group).  Tiles are walked in bands of kBandRows output rows: inside a band the m tile
+// runs fastest, then the n tile, so the CTAs running at any moment share a few A row-blocks and W column-blocks
+// (both stay L2-resident while the band sweeps all of N) and A is fetched from HBM once instead of once per n tile.
+constexpr int kBandRows = 2048;
+__device__ __forceinline__ void decode_tile(int tile, int m_tiles, int n_tiles, int band_m, int* mt, int* nt, int* grp) {
+  const int per_grp = m_tiles * n_tiles;
+  *grp = tile / per_grp;
+  const int t = tile - *grp * per_grp;
+  const int band = t / (band_m * n_tiles);
+  const int m_lo = band * band_m;
+  const int bm = min(band_m, m_tiles - m_lo);
+  const int r = t - band * band_m * n_tiles;
+  *nt = r / bm;
+  *mt = m_lo + r - *nt * bm;
+}
+
+// CG = 1: one CTA per 128 x BN tile.  CG = 2: a CTA PAIR (cluster of 2 on one TPC) per 256 x BN tile --
+// each CTA stages its own 128 A rows and BN/2 of the W rows, the leader issues tcgen05.mma.cta_group::2
+// (M = 256), so every CTA reads half as much B from shared memory / L2 per FLOP as in the CG = 1 form.
+template <int EPI, typename TOut, int CG>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, GemmArgs g,
                int BN, int stages, int n_tiles) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int stage_bytes = A_STAGE_BYTES + BN * BK * 2;
+  constexpr int BMT = BM * CG;                         // output rows per tile
+  const int BNL = BN / CG;                             // W rows (output columns) this CTA stages
+  const int stage_bytes = A_STAGE_BYTES + BNL * BK * 2;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + stages * stage_bytes);
   uint64_t* empty = full + kMaxStages;
   uint64_t* tfull = empty + kMaxStages;
@@ -36,11 +57,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = CG == 2 ? static_cast<int>(ptx::cluster_ctarank()) : 0;
+  const int worker = blockIdx.x / CG, n_workers = gridDim.x / CG;
   // the device-side count bounds the token dimension: output rows (NT / NN) or the reduction (TN)
   const int dyn = g.m_dyn ? __ldg(g.m_dyn) : 0x7fffffff;
   const int M = g.a_mn ? g.M : min(g.M, dyn);
   const int Kred = g.a_mn ? min(g.K, dyn) : g.K;
-  const int m_tiles = (M + BM - 1) / BM;
+  const int m_tiles = (M + BMT - 1) / BMT;
   const int total_tiles = g.groups * m_tiles * n_tiles;
   const int num_kb = (Kred + BK - 1) / BK;
 
@@ -55,39 +78,63 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], 4);
+      ptx::mbar_init(&tempty[s], 4 * CG);              // the leader waits for the epilogue warps of BOTH CTAs
     }
     ptx::fence_barrier_init();
   }
-  if (warp == 2) ptx::tmem_alloc<kTmemCols>(tmem_slot);
+  if (warp == 2) {
+    if (CG == 2) ptx::tmem_alloc_pair<kTmemCols>(tmem_slot);
+    else ptx::tmem_alloc<kTmemCols>(tmem_slot);
+  }
   ptx::tc_fence_before();
-  __syncthreads();
+  if (CG == 2) ptx::cluster_sync();
+  else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ------------------------------------------------------------ TMA producer
+    // ------------------------------------------------------------ TMA producer (every CTA)
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int mt = tile % m_tiles, rest = tile / m_tiles, nt = rest % n_tiles, grp = rest / n_tiles;
+      for (int tile = worker; tile < total_tiles; tile += n_workers) {
+        int mt, nt, grp;
+        decode_tile(tile, m_tiles, n_tiles, kBandRows / BMT, &mt, &nt, &grp);
         const int ga = g.sa ? grp : 0, gw = g.sw ? grp : 0;
+        const int m0 = mt * BMT + rank * BM, n0 = nt * BN + rank * BNL;
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(&empty[s], ph ^ 1);
           uint8_t* sa = smem + s * stage_bytes;
-          ptx::mbar_arrive_expect_tx(&full[s], stage_bytes);
-          if (!g.a_mn) {
-            ptx::tma_load_3d(sa, &tmA, &full[s], kb * BK, mt * BM, ga);
-          } else {                                     // A stored [K, M]: two 64-column atoms of 64 k-rows
-            ptx::tma_load_3d(sa, &tmA, &full[s], mt * BM, kb * BK, ga);
-            ptx::tma_load_3d(sa + 8192, &tmA, &full[s], mt * BM + 64, kb * BK, ga);
-          }
-          if (!g.b_mn) {
-            ptx::tma_load_3d(sa + A_STAGE_BYTES, &tmW, &full[s], kb * BK, nt * BN, gw);
-          } else {                                     // W stored [K, N]: BN/64 atoms
-            for (int at = 0; at < BN / 64; ++at)
-              ptx::tma_load_3d(sa + A_STAGE_BYTES + at * 8192, &tmW, &full[s], nt * BN + at * 64, kb * BK, gw);
+          if (CG == 1) {
+            ptx::mbar_arrive_expect_tx(&full[s], stage_bytes);
+            if (!g.a_mn) {
+              ptx::tma_load_3d(sa, &tmA, &full[s], kb * BK, m0, ga);
+            } else {                                   // A stored [K, M]: two 64-column atoms of 64 k-rows
+              ptx::tma_load_3d(sa, &tmA, &full[s], m0, kb * BK, ga);
+              ptx::tma_load_3d(sa + 8192, &tmA, &full[s], m0 + 64, kb * BK, ga);
+            }
+            if (!g.b_mn) {
+              ptx::tma_load_3d(sa + A_STAGE_BYTES, &tmW, &full[s], kb * BK, n0, gw);
+            } else {                                   // W stored [K, N]: BN/64 atoms
+              for (int at = 0; at < BNL / 64; ++at)
+                ptx::tma_load_3d(sa + A_STAGE_BYTES + at * 8192, &tmW, &full[s], n0 + at * 64, kb * BK, gw);
+            }
+          } else {
+            // all bytes of the pair are counted on the LEADER's full barrier
+            if (rank == 0) ptx::mbar_arrive_expect_tx(&full[s], stage_bytes * CG);
+            const uint32_t fb = ptx::mapa(ptx::smem_u32(&full[s]), 0);
+            if (!g.a_mn) {
+              ptx::tma_load_3d_pair(sa, &tmA, fb, kb * BK, m0, ga);
+            } else {
+              ptx::tma_load_3d_pair(sa, &tmA, fb, m0, kb * BK, ga);
+              ptx::tma_load_3d_pair(sa + 8192, &tmA, fb, m0 + 64, kb * BK, ga);
+            }
+            if (!g.b_mn) {
+              ptx::tma_load_3d_pair(sa + A_STAGE_BYTES, &tmW, fb, kb * BK, n0, gw);
+            } else {
+              for (int at = 0; at < BNL / 64; ++at)
+                ptx::tma_load_3d_pair(sa + A_STAGE_BYTES + at * 8192, &tmW, fb, n0 + at * 64, kb * BK, gw);
+            }
           }
           if (++s == stages) { s = 0; ph ^= 1; }
         }
@@ -95,19 +142,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0) {
-      const uint32_t idesc = ptx::umma_idesc_bf16(BM, BN, g.a_mn, g.b_mn);
+    // ------------------------------------------------------------ MMA issuer (one thread of the leader CTA)
+    if (lane == 0 && rank == 0) {
+      const uint32_t idesc = ptx::umma_idesc_bf16(BMT, BN, g.a_mn, g.b_mn);
       int s = 0, it = 0;
       uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      for (int tile = worker; tile < total_tiles; tile += n_workers, ++it) {
         const int as = it & 1;
         const uint32_t aph = (it >> 1) & 1;
         ptx::mbar_wait(&tempty[as], aph ^ 1);          // epilogue has drained this accumulator stage
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * kAccStride;
         for (int kb = 0; kb < num_kb; ++kb) {
-          ptx::mbar_wait(&full[s], ph);                // TMA bytes have landed
+          ptx::mbar_wait(&full[s], ph);                // TMA bytes have landed (in both CTAs)
           ptx::tc_fence_after();
           const uint32_t a_addr = ptx::smem_u32(smem + s * stage_bytes);
           const uint32_t b_addr = a_addr + A_STAGE_BYTES;
@@ -119,13 +166,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                                        : ptx::umma_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
             const uint64_t bd = g.b_mn ? ptx::umma_smem_desc(b_addr + k * 2048, 8192, 1024)
                                        : ptx::umma_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
-            ptx::umma_bf16_ss(d_tmem, ad, bd, idesc, (kb | k) != 0);
+            if (CG == 2) ptx::umma_bf16_ss_pair(d_tmem, ad, bd, idesc, (kb | k) != 0);
+            else ptx::umma_bf16_ss(d_tmem, ad, bd, idesc, (kb | k) != 0);
           }
-          ptx::umma_commit(&empty[s]);                 // frees the smem slot when these MMAs retire
+          if (CG == 2) ptx::umma_commit_pair(&empty[s]);   // frees the smem slot of both CTAs when these MMAs retire
+          else ptx::umma_commit(&empty[s]);
           if (++s == stages) { s = 0; ph ^= 1; }
         }
-        if (num_kb > 0) ptx::umma_commit(&tfull[as]);  // accumulator complete -> epilogue
-        else ptx::mbar_arrive(&tfull[as]);             // empty reduction: the epilogue writes zeros
+        if (num_kb > 0) {                              // accumulator complete -> epilogue (of both CTAs)
+          if (CG == 2) ptx::umma_commit_pair(&tfull[as]);
+          else ptx::umma_commit(&tfull[as]);
+        } else {                                       // empty reduction: the epilogue writes zeros
+          ptx::mbar_arrive(&tfull[as]);
+          if (CG == 2) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tfull[as]), 1));
+        }
       }
     }
     __syncwarp();
@@ -133,13 +187,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ------------------------------------------------------------ epilogue warps (TMEM -> regs -> HBM)
     const int q = warp & 3;                            // TMEM lane quadrant this warp may read
     int it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int mt = tile % m_tiles, rest = tile / m_tiles, nt = rest % n_tiles, grp = rest / n_tiles;
+    for (int tile = worker; tile < total_tiles; tile += n_workers, ++it) {
+      int mt, nt, grp;
+      decode_tile(tile, m_tiles, n_tiles, kBandRows / BMT, &mt, &nt, &grp);
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       ptx::mbar_wait(&tfull[as], aph);
       ptx::tc_fence_after();
-      const int row = mt * BM + q * 32 + lane;
+      const int row = mt * BMT + rank * BM + q * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * kAccStride;
       LseAcc la;
       int tgt = -1;
@@ -188,12 +243,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         g.partials[static_cast<long>(row) * g.n_tiles + nt] = make_float4(la.m, la.s, __int_as_float(la.arg), la.tz);
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&tempty[as]);
+      if (lane == 0) {
+        if (CG == 2) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tempty[as]), 0));
+        else ptx::mbar_arrive(&tempty[as]);
+      }
     }
   }
   ptx::tc_fence_before();
-  __syncthreads();
-  if (warp == 2) ptx::tmem_dealloc<kTmemCols>(tmem_base);
+  if (CG == 2) ptx::cluster_sync();
+  else __syncthreads();
+  if (warp == 2) {
+    if (CG == 2) ptx::tmem_dealloc_pair<kTmemCols>(tmem_base);
+    else ptx::tmem_dealloc<kTmemCols>(tmem_base);
+  }
 }
 }  // namespace tc
 
@@ -351,44 +413,88 @@ int make_tmap_bf16_3d(CUtensorMap* tm, const void* base, long d0, long d1, long 
   return TNT_OK;
 }
 
-static int pick_bn(int M, int N, int groups, bool b_mn = false) {
-  const int m_tiles = (M + tc::BM - 1) / tc::BM;
+static int g_cta_group = 0;   // test hook: 0 = automatic, 1 / 2 = force the single-CTA / CTA-pair kernel
+
+// tile shape the tcgen05 dispatcher uses: CTA-pair 256 x 256 tiles when the problem fills the 74 SM pairs for
+// several waves, else single-CTA 128 x BN with BN shrunk until the grid covers the SMs
+static void pick_tile(int M, int N, int groups, bool b_mn, int* bn_out, int* cg_out) {
   const int sms = num_sms();
+  if (g_cta_group != 1 && M >= 256 && N >= 256) {
+    const long pair_tiles = static_cast<long>(groups) * ((M + 255) / 256) * ((N + 255) / 256);
+    if (g_cta_group == 2 || pair_tiles >= 4L * (sms / 2)) {
+      *bn_out = 256;
+      *cg_out = 2;
+      return;
+    }
+  }
+  *cg_out = 1;
+  const int m_tiles = (M + tc::BM - 1) / tc::BM;
   const int cands[4] = {256, 128, 64, 32};
   const int last = b_mn ? 2 : 3;                       // an MN-major W tile is built from 64-column atoms
   for (int i = 0; i <= last; ++i) {
     const int bn = cands[i];
     if (i < last && N <= cands[i + 1]) continue;       // tile would be mostly padding
     const long tiles = static_cast<long>(groups) * m_tiles * ((N + bn - 1) / bn);
-    if (tiles >= sms || i == last) return bn;
+    if (tiles >= sms || i == last) {
+      *bn_out = bn;
+      return;
+    }
   }
-  return cands[last];
+  *bn_out = cands[last];
 }
 
-int gemm_tile_n(int dtype, int M, int N) { return dtype == TNT_BF16 ? pick_bn(M, N, 1) : simt::TN; }
+int gemm_tile_n(int dtype, int M, int N) {
+  if (dtype != TNT_BF16) return simt::TN;
+  int bn, cg;
+  pick_tile(M, N, 1, false, &bn, &cg);
+  return bn;
+}
 
-template <int EPI, typename TOut>
-static int launch_tc(const GemmArgs& g, int BN, cudaStream_t st) {
+template <int EPI, typename TOut, int CG>
+static int launch_tc_cg(const GemmArgs& g, int BN, cudaStream_t st) {
   CUtensorMap tmA, tmW;
+  const int BNL = BN / CG;
   if (g.a_mn) TNT_TRY(make_tmap_bf16(&tmA, g.a, g.M, g.K, g.lda, g.groups, g.sa, 64));
   else TNT_TRY(make_tmap_bf16(&tmA, g.a, g.K, g.M, g.lda, g.groups, g.sa, tc::BM));
   if (g.b_mn) TNT_TRY(make_tmap_bf16(&tmW, g.w, g.N, g.K, g.ldw, g.groups, g.sw, 64));
-  else TNT_TRY(make_tmap_bf16(&tmW, g.w, g.K, g.N, g.ldw, g.groups, g.sw, BN));
-  const int stage_bytes = tc::A_STAGE_BYTES + BN * tc::BK * 2;
+  else TNT_TRY(make_tmap_bf16(&tmW, g.w, g.K, g.N, g.ldw, g.groups, g.sw, BNL));
+  const int stage_bytes = tc::A_STAGE_BYTES + BNL * tc::BK * 2;
   const int stages = std::min(tc::kMaxStages, (tc::kSmemBudget - 2048) / stage_bytes);
   const int smem = stages * stage_bytes + 1024 + 512;
   const int n_tiles = (g.N + BN - 1) / BN;
-  const long tiles = static_cast<long>(g.groups) * ((g.M + tc::BM - 1) / tc::BM) * n_tiles;
-  const int grid = static_cast<int>(std::min<long>(tiles, num_sms()));
-  auto kern = tc::gemm_tc_kernel<EPI, TOut>;
+  const long tiles = static_cast<long>(g.groups) * ((g.M + tc::BM * CG - 1) / (tc::BM * CG)) * n_tiles;
+  const int grid = CG * static_cast<int>(std::min<long>(tiles, num_sms() / CG));
+  auto kern = tc::gemm_tc_kernel<EPI, TOut, CG>;
   static bool attr_set = false;   // per instantiation
   if (!attr_set) {
     TNT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBudget + 4096));
     attr_set = true;
   }
-  kern<<<grid, tc::kThreads, smem, st>>>(tmA, tmW, g, BN, stages, n_tiles);
+  if (CG == 1) {
+    kern<<<grid, tc::kThreads, smem, st>>>(tmA, tmW, g, BN, stages, n_tiles);
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(tc::kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CG;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    TNT_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, g, BN, stages, n_tiles));
+  }
   TNT_LAUNCHED();
   return TNT_OK;
+}
+
+template <int EPI, typename TOut>
+static int launch_tc(const GemmArgs& g, int BN, int CG, cudaStream_t st) {
+  if (CG == 2) return launch_tc_cg<EPI, TOut, 2>(g, BN, st);
+  return launch_tc_cg<EPI, TOut, 1>(g, BN, st);
 }
 
 template <int EPI, typename TIn, typename TOut>
@@ -400,10 +506,10 @@ static int launch_simt(const GemmArgs& g, cudaStream_t st) {
 }
 
 template <int EPI>
-static int dispatch_dtype(const GemmArgs& g, int dt_in, int dt_out, int BN, bool force_simt, cudaStream_t st) {
+static int dispatch_dtype(const GemmArgs& g, int dt_in, int dt_out, int BN, int CG, bool force_simt, cudaStream_t st) {
   if (dt_in == TNT_BF16 && !force_simt) {
-    if (dt_out == TNT_BF16) return launch_tc<EPI, bf16>(g, BN, st);
-    return launch_tc<EPI, float>(g, BN, st);
+    if (dt_out == TNT_BF16) return launch_tc<EPI, bf16>(g, BN, CG, st);
+    return launch_tc<EPI, float>(g, BN, CG, st);
   }
   if (dt_in == TNT_BF16) {
     if (dt_out == TNT_BF16) return launch_simt<EPI, bf16, bf16>(g, st);
@@ -454,24 +560,24 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
                                ((epi != EPI_RESIDUAL && epi != EPI_RELU_BWD) ||
                                 (aligned16(p->residual) && p->ldr % vec == 0 && g.sres % vec == 0)));
   const bool use_tc = p->dtype_in == TNT_BF16 && !g_force_simt;
-  int BN = simt::TN;
+  int BN = simt::TN, CG = 1;
   if (use_tc) {
     TNT_CHECK_ALIGN(aligned16(p->a) && aligned16(p->w) && p->lda % 8 == 0 && p->ldw % 8 == 0 && g.sa % 8 == 0 &&
                         g.sw % 8 == 0,
                     "linear(bf16): A / W must be 16-byte aligned with leading dimensions multiple of 8 (lda=%ld ldw=%ld)",
                     (long)p->lda, (long)p->ldw);
-    BN = pick_bn(g.M, g.N, g.groups, g.b_mn != 0);
+    pick_tile(g.M, g.N, g.groups, g.b_mn != 0, &BN, &CG);
   }
   g.n_tiles = (g.N + BN - 1) / BN;
   if (n_tiles_out) *n_tiles_out = g.n_tiles;
   switch (epi) {
-    case EPI_NONE: return dispatch_dtype<EPI_NONE>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
-    case EPI_RELU: return dispatch_dtype<EPI_RELU>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
-    case EPI_GLU: return dispatch_dtype<EPI_GLU>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
-    case EPI_RESIDUAL: return dispatch_dtype<EPI_RESIDUAL>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
-    case EPI_LSE: return dispatch_dtype<EPI_LSE>(g, p->dtype_in, TNT_F32, BN, g_force_simt, st);
-    case EPI_RELU_BWD: return dispatch_dtype<EPI_RELU_BWD>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
-    case EPI_SMGRAD: return dispatch_dtype<EPI_SMGRAD>(g, p->dtype_in, p->dtype_out, BN, g_force_simt, st);
+    case EPI_NONE: return dispatch_dtype<EPI_NONE>(g, p->dtype_in, p->dtype_out, BN, CG, g_force_simt, st);
+    case EPI_RELU: return dispatch_dtype<EPI_RELU>(g, p->dtype_in, p->dtype_out, BN, CG, g_force_simt, st);
+    case EPI_GLU: return dispatch_dtype<EPI_GLU>(g, p->dtype_in, p->dtype_out, BN, CG, g_force_simt, st);
+    case EPI_RESIDUAL: return dispatch_dtype<EPI_RESIDUAL>(g, p->dtype_in, p->dtype_out, BN, CG, g_force_simt, st);
+    case EPI_LSE: return dispatch_dtype<EPI_LSE>(g, p->dtype_in, TNT_F32, BN, CG, g_force_simt, st);
+    case EPI_RELU_BWD: return dispatch_dtype<EPI_RELU_BWD>(g, p->dtype_in, p->dtype_out, BN, CG, g_force_simt, st);
+    case EPI_SMGRAD: return dispatch_dtype<EPI_SMGRAD>(g, p->dtype_in, p->dtype_out, BN, CG, g_force_simt, st);
   }
   set_error("linear: unknown epilogue %d", epi);
   return TNT_ERR_ARG;
@@ -483,3 +589,4 @@ extern "C" int tnt_linear_fwd(const tnt_linear_params* p, tnt_stream stream) {
   return tnt::launch_gemm(p, -1, nullptr, nullptr, tnt::as_stream(stream));
 }
 extern "C" void tnt_debug_force_simt_gemm(int on) { tnt::gemm_force_simt(on != 0); }
+extern "C" void tnt_debug_gemm_cta_group(int cg) { tnt::g_cta_group = (cg == 1 || cg == 2) ? cg : 0; }

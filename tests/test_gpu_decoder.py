@@ -121,6 +121,26 @@ def test_full_size_bf16_vs_oracle(full_model):
     assert abs(out[0].item() - loss_o.item()) < 2e-2 * abs(loss_o.item())
 
 
+def test_full_size_bf16_generation_vs_oracle(full_model):
+    """bf16 greedy generation (decode-step attention kernel, DynamicConv ring, cached K/V): the oracle, teacher-forced
+    on the ids the engine picked, must give those tokens the same log-probs (2e-2) and rank them top-1 up to bf16 ties."""
+    cfg, sd = full_model
+    prev, tgt, ctx = synth.make_batch(6, 32, 50265, ('image', 'article'), seed=91)
+    dec = make_decoder(cfg, sd, torch.bfloat16)
+    L = 8
+    lp, ids = dec.generate(prev[:, :1].cuda(), cuda_ctx(ctx), gen_len=L, eos=-1, trim=False)
+    ids_c = ids.cpu()
+    Xo, _ = O.decoder_forward(ids_c[:, :-1], ctx, sd, 16, cfg['cutoffs'], cfg['sources'])
+    lpo = O.adaptive_log_prob(Xo, sd, cfg['cutoffs'])
+    picked = lpo.gather(2, ids_c[:, 1:, None])[:, :, 0]
+    assert (picked - lp.cpu()).abs().max().item() < 2e-2 * max(1.0, picked.abs().max().item())
+    assert (lpo.max(-1).values - picked).max().item() < 5e-2       # the engine's choice is the oracle's top-1 up to a bf16 tie
+    # same ids through the engine's own teacher-forced bf16 path
+    X, _ = dec(ids[:, :-1], cuda_ctx(ctx))
+    full = dec.get_normalized_probs((X, None))
+    assert (full.gather(2, ids[:, 1:, None])[:, :, 0] - lp).abs().max().item() < 2e-2 * max(1.0, picked.abs().max().item())
+
+
 def test_loss_properties_full_vocab(full_model):
     """size-independent checks at full vocabulary: log-probs normalise, NLL == -sum picked log-prob
     with the reference's in-cluster ignore_index quirk (adaptive_loss.py:59 with softmax.py:162)."""

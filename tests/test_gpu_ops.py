@@ -110,6 +110,47 @@ def test_tc_matches_simt(ops):
     assert rel_err(tc, sm) < 1e-5
 
 
+@pytest.mark.parametrize('M,N,K', [(256, 256, 64), (300, 520, 200), (1000, 777, 1024), (2048, 5002, 1024), (4096, 2048, 512)])
+def test_linear_cta_pair(ops, M, N, K):
+    """The CTA-pair (cta_group::2, 256 x 256 tiles) kernel, forced, against the single-CTA kernel and fp64:
+    NT with every epilogue, NN, TN (ragged M / N / K: OOB rows are TMA zero fill)."""
+    from news_image_caption_b200 import _lib
+    g = torch.Generator().manual_seed(M + 7 * N + K)
+    a = torch.randn(M, K, generator=g).bfloat16()
+    K8 = K
+    w = (torch.randn(N, K8, generator=g) / K ** 0.5).bfloat16()
+    b = torch.randn(N, generator=g)
+    r = torch.randn(M, N, generator=g).bfloat16()
+    z = a.double() @ w.double().t() + b.double()
+    L = _lib.lib()
+    one = ops.linear(a.cuda(), w.cuda(), b.cuda(), out_dtype=torch.float32)
+    L.tnt_debug_gemm_cta_group(2)
+    try:
+        two = ops.linear(a.cuda(), w.cuda(), b.cuda(), out_dtype=torch.float32)
+        assert rel_err(two, z) < 8e-3
+        assert rel_err(two, one) < 1e-5
+        assert rel_err(ops.linear(a.cuda(), w.cuda(), b.cuda(), _lib.EPI_RELU), z.relu()) < 1e-2
+        assert rel_err(ops.linear(a.cuda(), w.cuda(), b.cuda(), _lib.EPI_RESIDUAL, residual=r.cuda()), z + r.double()) < 1e-2
+        if N % 2 == 0:
+            wi = ops.wn_fold(w.float().cuda(), None, glu_interleave=True, dtype=torch.bfloat16)
+            bi = ops.glu_interleave_bias(b.cuda())
+            assert rel_err(ops.linear(a.cuda(), wi, bi, _lib.EPI_GLU), F.glu(z, dim=-1)) < 1e-2
+        if N % 8 == 0 and K % 8 == 0:
+            # backward layouts: dX = dY . W (NN), dW = dY^T . X (TN)
+            dy, wkn = a, (torch.randn(K, N, generator=g) / K ** 0.5).bfloat16()
+            assert rel_err(ops.linear(dy.cuda(), wkn.cuda(), layout=_lib.LAYOUT_NN), dy.double() @ wkn.double()) < 8e-3
+            x = torch.randn(M, N, generator=g).bfloat16()
+            dw = ops.linear(dy.cuda(), x.cuda(), layout=_lib.LAYOUT_TN, out_dtype=torch.float32)
+            assert rel_err(dw, dy.double().t() @ x.double()) < 8e-3
+        # the log-sum-exp epilogue (adaptive-softmax clusters) on the pair kernel
+        tgt = torch.randint(0, N, (M,), generator=g)
+        mx, se, arg, picked = ops.lse(a.cuda(), w.cuda(), b.cuda(), tgt.cuda())
+        assert rel_err(mx + se.log(), torch.logsumexp(z, -1)) < 1e-3
+        assert rel_err(picked, z.gather(1, tgt[:, None])[:, 0]) < 1e-2
+    finally:
+        L.tnt_debug_gemm_cta_group(0)
+
+
 def test_wn_fold(ops):
     g = torch.Generator().manual_seed(2)
     v, gg = torch.randn(64, 40, generator=g), torch.randn(64, 1, generator=g)
@@ -201,6 +242,36 @@ def test_xattn_golden(ops, dtype):
         out = F.linear(o.float().cpu(), sd['out_proj.weight'], sd['out_proj.bias'])
         assert rel_err(out, c['out']) < TOL[dtype]
         assert rel_err(w, c['weights']) < TOL[dtype]
+
+
+@pytest.mark.parametrize('B,S', [(5, 514), (3, 51), (2, 6), (9, 1000)])
+def test_xattn_decode_step(ops, B, S):
+    """T == 1 (one query per caption and head: the `_generate` step): the HBM-streaming decode kernel vs the
+    oracle's attention core; ragged padding incl. captions whose only live keys are the 2 trailing extra rows."""
+    g = torch.Generator().manual_seed(B * 1000 + S)
+    E, H = 1024, 16
+    q, k, v = (torch.randn(n, B, E, generator=g).bfloat16() for n in (1, S, S))
+    n = torch.randint(0, S - 1, (B,), generator=g)
+    n[0], n[-1] = S - 2, 0                                          # nothing masked / everything but the extras masked
+    mask = torch.arange(S - 2)[None] >= n[:, None]                  # covers keys [0, S-2): the last two rows are extras
+    sd = {'in_proj_bias': torch.zeros(3 * E), 'in_proj_weight': torch.eye(E).repeat(3, 1),
+          'out_proj.weight': torch.eye(E), 'out_proj.bias': torch.zeros(E)}
+    full_mask = torch.cat([mask, torch.zeros(B, 2, dtype=torch.bool)], 1)
+    ref, _ = O.mha_attend(q.float(), k.float(), v.float(), full_mask[:, :S - 2], sd, '', H)
+    lse = torch.empty(B, H, 1, device='cuda')
+    o, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, 64 ** -0.5, pad_mask=mask.cuda(), mask_S=S - 2, lse=lse)
+    assert rel_err(o, ref) < 1e-2
+    # log-sum-exp of the scaled masked scores (what the backward consumes), vs plain torch
+    sc = torch.einsum('bhd,sbhd->bhs', q[0].float().view(B, H, 64), k.float().view(S, B, H, 64)) * 64 ** -0.5
+    sc = sc.masked_fill(full_mask[:, None, :], float('-inf'))
+    assert rel_err(lse[:, :, 0], torch.logsumexp(sc, -1)) < 1e-3
+    from news_image_caption_b200 import _lib
+    _lib.lib().tnt_debug_force_simt_attention(1)
+    try:
+        o2, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, 64 ** -0.5, pad_mask=mask.cuda(), mask_S=S - 2)
+    finally:
+        _lib.lib().tnt_debug_force_simt_attention(0)
+    assert rel_err(o, o2) < 1e-2
 
 
 def test_xattn_full_size(ops):
