@@ -331,13 +331,15 @@ def main():
     if gen:
         # dominant kernel of a decoding step: cross-attention over the cached article K/V (1 query per head):
         # algorithmic bytes = K and V rows of this layer for every caption, (S+2) * 2 * d * 2 B, + q/out
-        byts = B_PER_GPU * ((S_ART + 2) * 2 * 1024 * 2 + 2 * 1024 * 2)
+        # for every LIVE key (padded article positions are never fetched; + the bias_k/v row and the zero row)
+        live = int((~ctx['article_mask']).sum()) + 2 * B_PER_GPU
+        byts = live * 2 * 1024 * 2 + B_PER_GPU * 2 * 1024 * 2
         x_ms = xs_ms.value / max(xs_n.value, 1)
         ach = byts / (x_ms * 1e-3) / 1e9 if x_ms > 0 else 0.0
         roofline = {'bound': 'hbm', 'kernel': 'decode-step cross-attention over the cached article K/V (one layer)',
                     'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': None,
                     'peak_source': which + ' hbm_gbs', 'bytes_per_launch': byts, 'ms_per_launch': x_ms,
-                    'launches_timed': xs_n.value, 'note': 'timed on the eager step 0 of every generate call (steps 1.. replay a CUDA graph)',
+                    'launches_timed': xs_n.value, 'live_keys_per_caption': live / B_PER_GPU, 'note': 'timed on the eager step 0 of every generate call (steps 1.. replay a CUDA graph)',
                     'kv_proj_gemm_tflops': achieved, 'kv_proj_ms': gemm_ms}
     cpu = None
     if not args.no_cpu_baseline and gen:

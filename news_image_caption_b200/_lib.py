@@ -143,6 +143,7 @@ _SIGS = {
     'tnt_bert_adam_step': (i32, [C.POINTER(AdamParams), vp]),
     'tnt_debug_force_simt_gemm': (None, [i32]),
     'tnt_debug_gemm_cta_group': (None, [i32]),
+    'tnt_debug_pdl': (None, [i32]),
     'tnt_debug_force_simt_attention': (None, [i32]),
     'tnt_debug_force_simt_attention_bwd': (None, [i32]),
 }

@@ -13,6 +13,7 @@ namespace {
 // merge the per-N-tile partials of one row: one warp per row
 __global__ void __launch_bounds__(256) lse_finish_kernel(const float4* partials, int n_tiles, int M, const int* m_dyn,
                                                          const int* row_map, float4* stats) {
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int Me = m_dyn ? min(M, *m_dyn) : M;
@@ -221,7 +222,7 @@ int lse_gemm(const void* x, long ldx, const void* w, long ldw, const float* bias
   LseExtra ex = {target, partials, n_lse, side, side_ld};
   int n_tiles = 0;
   TNT_TRY(launch_gemm(&lp, EPI_LSE, &ex, &n_tiles, st));
-  lse_finish_kernel<<<(M + 7) / 8, 256, 0, st>>>(partials, n_tiles, M, m_dyn, row_map, stats);
+  TNT_CUDA(launch_pdl(lse_finish_kernel, dim3((M + 7) / 8), dim3(256), 0, st, 1, partials, n_tiles, M, m_dyn, row_map, stats));
   TNT_LAUNCHED();
   return TNT_OK;
 }

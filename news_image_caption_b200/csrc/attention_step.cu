@@ -42,6 +42,7 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(tnt_xattn_param
   __shared__ uint8_t sm_mask[kMaxKeys];
   __shared__ uint16_t sm_live[kMaxKeys];
   __shared__ int sm_nlive;
+  pdl_wait();
   const int b = blockIdx.x, hg = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int h = hg * kHeadsPerCta + (lane >> 2), d0 = (lane & 3) * 16;
@@ -168,7 +169,7 @@ bool xattn_step_supported(const tnt_xattn_params* p) {
 
 int xattn_fwd_step(const tnt_xattn_params* p, cudaStream_t st) {
   dim3 grid(p->B, p->H / kHeadsPerCta);
-  xattn_step_kernel<<<grid, kWarps * 32, 0, st>>>(*p);
+  TNT_CUDA(launch_pdl(xattn_step_kernel, grid, dim3(kWarps * 32), 0, st, 1, *p));
   TNT_LAUNCHED();
   return TNT_OK;
 }

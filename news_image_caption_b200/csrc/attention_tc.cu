@@ -92,6 +92,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   ptx::tc_fence_after();
   const uint32_t tmem = bar->tmem;
   const int HP = a.H >> 1;
+  pdl_wait();                       // prologue above overlaps the preceding kernel's tail (PDL)
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -338,7 +339,7 @@ int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st) {
     attr = true;
   }
   const int grid = std::min(a.n_items, num_sms());
-  atc::xattn_tc_kernel<<<grid, atc::kThreads, atc::SMEM_BYTES, st>>>(tmQ, tmK, tmV, a);
+  TNT_CUDA(launch_pdl(atc::xattn_tc_kernel, dim3(grid), dim3(atc::kThreads), atc::SMEM_BYTES, st, 1, tmQ, tmK, tmV, a));
   TNT_LAUNCHED();
   return TNT_OK;
 }

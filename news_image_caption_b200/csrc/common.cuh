@@ -54,6 +54,38 @@ void prof_end(int id, cudaStream_t st);
     if (s__ != TNT_OK) return s__; \
   } while (0)
 
+// Programmatic dependent launch (PDL): a kernel launched through launch_pdl() may start while its predecessor in
+// the stream is still draining -- its prologue (barrier init, TMEM allocation, descriptor prefetch) overlaps the
+// predecessor's tail -- and MUST execute pdl_wait() before its first global-memory access (and before any write
+// a predecessor could still read).  Kernels that never call pdl_wait() must be launched the plain way.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster_x,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[2];
+  int n = 0;
+  if (pdl_enabled()) {
+    at[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (cluster_x > 1) {
+    at[n].id = cudaLaunchAttributeClusterDimension;
+    at[n].val.clusterDim.x = cluster_x;
+    at[n].val.clusterDim.y = 1;
+    at[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  cfg.attrs = at;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 inline size_t dtype_size(int dt) { return dt == TNT_BF16 ? 2 : 4; }
 inline int num_sms() {
@@ -70,6 +102,13 @@ inline cudaStream_t as_stream(tnt_stream s) { return reinterpret_cast<cudaStream
 
 // ------------------------------------------------------------------ device side
 using bf16 = __nv_bfloat16;
+
+// PDL: block until the preceding kernel of the stream has completed and its writes are visible (no-op for a plain
+// launch), then let the NEXT kernel's CTAs be scheduled as soon as SM resources free up.
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
 
 template <typename T> struct Vec8;   // 8 elements = 128 bit (bf16) / 2 x 128 bit (fp32)
 

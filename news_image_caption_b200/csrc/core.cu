@@ -1,5 +1,6 @@
 // Library-wide plumbing: error string, launch counter, device check.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <atomic>
 #include <mutex>
@@ -18,6 +19,14 @@ void set_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+static int g_pdl = -1;      // -1: read TNT_PDL from the environment on first use (default on)
+bool pdl_enabled() {
+  if (g_pdl < 0) {
+    const char* e = getenv("TNT_PDL");
+    g_pdl = (e && e[0] == '0') ? 0 : 1;
+  }
+  return g_pdl != 0;
 }
 void count_launch(int n) { g_launches.fetch_add(static_cast<uint64_t>(n), std::memory_order_relaxed); }
 
@@ -66,6 +75,8 @@ extern "C" int tnt_device_check(void) {
   }
   return TNT_OK;
 }
+
+extern "C" void tnt_debug_pdl(int on) { tnt::g_pdl = on ? 1 : 0; }
 
 extern "C" void tnt_prof_enable(int on) {
   std::lock_guard<std::mutex> lk(tnt::g_prof_mu);

@@ -35,6 +35,7 @@ __device__ __forceinline__ void warp_softmax_taps(const T* lg, int K, float* out
 // smem: xs [(TT+K-1)][CC] fp32, taps [TT][HG][K] fp32
 template <typename T>
 __global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_params p, int CC, int HG) {
+  pdl_wait();
   extern __shared__ float sm[];
   const int K = p.K, R = p.C / p.H, B = p.B;
   const int b = blockIdx.x, c0 = blockIdx.y * CC, t0 = blockIdx.z * kTT;
@@ -97,6 +98,7 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_param
 // ring [K-1][B][C]; slot of step s = s mod (K-1).  One thread = 8 channels of one batch row.
 template <typename T>
 __global__ void __launch_bounds__(kThreads) dynconv_step_kernel(tnt_dynconv_step_params p) {
+  pdl_wait();
   extern __shared__ float sm[];               // taps [H][K] of this batch row
   const int K = p.K, R = p.C / p.H, b = blockIdx.x;
   const int pos = p.pos ? *p.pos : 0;
@@ -270,10 +272,10 @@ extern "C" int tnt_dynconv_fwd(const tnt_dynconv_params* p, tnt_stream stream) {
   dim3 grid(p->B, ngroups, (p->T + kTT - 1) / kTT);
   if (p->dtype == TNT_BF16) {
     TNT_TRY(set_smem(dynconv_fwd_kernel<bf16>, smem));
-    dynconv_fwd_kernel<bf16><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG);
+    TNT_CUDA(launch_pdl(dynconv_fwd_kernel<bf16>, grid, dim3(kThreads), smem, as_stream(stream), 1, *p, CC, HG));
   } else {
     TNT_TRY(set_smem(dynconv_fwd_kernel<float>, smem));
-    dynconv_fwd_kernel<float><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG);
+    TNT_CUDA(launch_pdl(dynconv_fwd_kernel<float>, grid, dim3(kThreads), smem, as_stream(stream), 1, *p, CC, HG));
   }
   TNT_LAUNCHED();
   return TNT_OK;
@@ -286,9 +288,9 @@ extern "C" int tnt_dynconv_step(const tnt_dynconv_step_params* p, tnt_stream str
   TNT_CHECK_ARG(p->logits && p->y && (p->ring || p->K == 1), "dynconv_step: null logits / y / ring");
   const size_t smem = static_cast<size_t>(p->H) * p->K * 4;
   if (p->dtype == TNT_BF16)
-    dynconv_step_kernel<bf16><<<p->B, kThreads, smem, as_stream(stream)>>>(*p);
+    TNT_CUDA(launch_pdl(dynconv_step_kernel<bf16>, dim3(p->B), dim3(kThreads), smem, as_stream(stream), 1, *p));
   else
-    dynconv_step_kernel<float><<<p->B, kThreads, smem, as_stream(stream)>>>(*p);
+    TNT_CUDA(launch_pdl(dynconv_step_kernel<float>, dim3(p->B), dim3(kThreads), smem, as_stream(stream), 1, *p));
   TNT_LAUNCHED();
   return TNT_OK;
 }

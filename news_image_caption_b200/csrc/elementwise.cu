@@ -11,6 +11,7 @@ constexpr int kWarps = 8;
 // nn.LayerNorm (decoder_flattened.py:245-268) and final* LayerNorm (transformer_v2.py:82-94).
 template <typename T, int MAXV>
 __global__ void __launch_bounds__(kWarps * 32) layernorm_fwd_kernel(tnt_layernorm_params p) {
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * kWarps + (threadIdx.x >> 5);
   if (row >= p.rows) return;
@@ -161,6 +162,7 @@ __global__ void __launch_bounds__(kWarps * 32) layernorm_bwd_kernel(tnt_layernor
 // adaptive.py:61-76 (pre-projected bands) + positional.py:167-211 + sum_text_field_embedder.py:117
 template <typename T>
 __global__ void __launch_bounds__(kWarps * 32) embed_kernel(tnt_embed_params p) {
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * kWarps + (threadIdx.x >> 5);      // row = t * B + b
   if (row >= p.T * p.B) return;
@@ -251,11 +253,11 @@ extern "C" int tnt_layernorm_fwd(const tnt_layernorm_params* p, tnt_stream strea
   cudaStream_t st = as_stream(stream);
   const bool small = p->C <= 1024;
   if (p->dtype == TNT_BF16) {
-    if (small) layernorm_fwd_kernel<bf16, 4><<<grid, kWarps * 32, 0, st>>>(*p);
-    else layernorm_fwd_kernel<bf16, 0><<<grid, kWarps * 32, 0, st>>>(*p);
+    if (small) TNT_CUDA(launch_pdl(layernorm_fwd_kernel<bf16, 4>, dim3(grid), dim3(kWarps * 32), 0, st, 1, *p));
+    else TNT_CUDA(launch_pdl(layernorm_fwd_kernel<bf16, 0>, dim3(grid), dim3(kWarps * 32), 0, st, 1, *p));
   } else {
-    if (small) layernorm_fwd_kernel<float, 4><<<grid, kWarps * 32, 0, st>>>(*p);
-    else layernorm_fwd_kernel<float, 0><<<grid, kWarps * 32, 0, st>>>(*p);
+    if (small) TNT_CUDA(launch_pdl(layernorm_fwd_kernel<float, 4>, dim3(grid), dim3(kWarps * 32), 0, st, 1, *p));
+    else TNT_CUDA(launch_pdl(layernorm_fwd_kernel<float, 0>, dim3(grid), dim3(kWarps * 32), 0, st, 1, *p));
   }
   TNT_LAUNCHED();
   return TNT_OK;
@@ -283,8 +285,8 @@ extern "C" int tnt_embed_fwd(const tnt_embed_params* p, tnt_stream stream) {
   const int rows = p->B * p->T;
   if (rows == 0) return TNT_OK;
   const int grid = (rows + kWarps - 1) / kWarps;
-  if (p->dtype == TNT_BF16) embed_kernel<bf16><<<grid, kWarps * 32, 0, as_stream(stream)>>>(*p);
-  else embed_kernel<float><<<grid, kWarps * 32, 0, as_stream(stream)>>>(*p);
+  if (p->dtype == TNT_BF16) TNT_CUDA(launch_pdl(embed_kernel<bf16>, dim3(grid), dim3(kWarps * 32), 0, as_stream(stream), 1, *p));
+  else TNT_CUDA(launch_pdl(embed_kernel<float>, dim3(grid), dim3(kWarps * 32), 0, as_stream(stream), 1, *p));
   TNT_LAUNCHED();
   return TNT_OK;
 }

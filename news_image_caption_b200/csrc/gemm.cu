@@ -55,18 +55,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tfull = empty + kMaxStages;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  float* sbias = reinterpret_cast<float*>(smem + stages * stage_bytes + 512);   // [2 accumulator stages][256], zero padded
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rank = CG == 2 ? static_cast<int>(ptx::cluster_ctarank()) : 0;
   const int worker = blockIdx.x / CG, n_workers = gridDim.x / CG;
-  // the device-side count bounds the token dimension: output rows (NT / NN) or the reduction (TN)
-  const int dyn = g.m_dyn ? __ldg(g.m_dyn) : 0x7fffffff;
-  const int M = g.a_mn ? g.M : min(g.M, dyn);
-  const int Kred = g.a_mn ? min(g.K, dyn) : g.K;
-  const int m_tiles = (M + BMT - 1) / BMT;
-  const int total_tiles = g.groups * m_tiles * n_tiles;
-  const int num_kb = (Kred + BK - 1) / BK;
 
+  // ---- prologue: touches no global data, so under PDL it overlaps the tail of the preceding kernel
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmW);
@@ -91,6 +86,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+
+  pdl_wait();                                          // the preceding kernel's outputs are visible from here on
+  // the device-side count bounds the token dimension: output rows (NT / NN) or the reduction (TN)
+  const int dyn = g.m_dyn ? *reinterpret_cast<const volatile int*>(g.m_dyn) : 0x7fffffff;
+  const int M = g.a_mn ? g.M : min(g.M, dyn);
+  const int Kred = g.a_mn ? min(g.K, dyn) : g.K;
+  const int m_tiles = (M + BMT - 1) / BMT;
+  const int total_tiles = g.groups * m_tiles * n_tiles;
+  const int num_kb = (Kred + BK - 1) / BK;
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (every CTA)
@@ -192,6 +196,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       decode_tile(tile, m_tiles, n_tiles, kBandRows / BMT, &mt, &nt, &grp);
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
+      // this tile's bias slice -> shared memory (one coalesced read per tile instead of 32 scalar loads per thread and
+      // chunk); the named barrier also orders it against the reads of tile it-2, which used the same slot
+      float* sb = sbias + as * 256;
+      if (g.bias) {
+        const float* bg = g.bias + grp * g.sbias + nt * BN;
+        for (int i = threadIdx.x - 64; i < BN; i += 128) sb[i] = (nt * BN + i < g.N) ? __ldg(bg + i) : 0.f;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
       ptx::mbar_wait(&tfull[as], aph);
       ptx::tc_fence_after();
       const int row = mt * BMT + rank * BM + q * 32 + lane;
@@ -219,8 +231,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (EPI == EPI_LSE) {
             if (g.bias) {
 #pragma unroll
-              for (int i = 0; i < 32; ++i)
-                if (n0 + i < g.N) acc[i] += __ldg(g.bias + n0 + i);
+              for (int i = 0; i < 32; ++i) acc[i] += sb[c * 32 + i];
             }
             if (n0 + 32 <= g.n_lse) {                  // common case: whole chunk inside the cluster
               la.add_chunk<32>(acc, n0, tgt);
@@ -235,7 +246,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               }
             }
           } else {
-            epilogue_store<EPI, TOut, 32>(g, grp, row, n0, acc);
+            epilogue_store<EPI, TOut, 32>(g, grp, row, n0, acc, g.bias ? sb + c * 32 : nullptr, true);
           }
         }
       }
@@ -339,7 +350,7 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(GemmArgs g) {
         g.partials[static_cast<long>(row) * g.n_tiles + blockIdx.x] =
             make_float4(la.m, la.s, __int_as_float(la.arg), la.tz);
     } else if (row < M) {
-      epilogue_store<EPI, TOut, 4>(g, grp, row, n0 + tx * 4, acc[i]);
+      epilogue_store<EPI, TOut, 4>(g, grp, row, n0 + tx * 4, acc[i], g.bias ? g.bias + grp * g.sbias + n0 + tx * 4 : nullptr, false);
     } else if (EPI != EPI_LSE && EPI != EPI_GLU && g.m_dyn && !g.a_mn && row < g.M) {
       zero_store<TOut, 4>(g, grp, row, n0 + tx * 4);
     }
@@ -459,8 +470,8 @@ static int launch_tc_cg(const GemmArgs& g, int BN, cudaStream_t st) {
   if (g.b_mn) TNT_TRY(make_tmap_bf16(&tmW, g.w, g.N, g.K, g.ldw, g.groups, g.sw, 64));
   else TNT_TRY(make_tmap_bf16(&tmW, g.w, g.K, g.N, g.ldw, g.groups, g.sw, BNL));
   const int stage_bytes = tc::A_STAGE_BYTES + BNL * tc::BK * 2;
-  const int stages = std::min(tc::kMaxStages, (tc::kSmemBudget - 2048) / stage_bytes);
-  const int smem = stages * stage_bytes + 1024 + 512;
+  const int stages = std::min(tc::kMaxStages, (tc::kSmemBudget - 4096) / stage_bytes);
+  const int smem = stages * stage_bytes + 1024 + 512 + 2048;     // ring + alignment slack + barriers + bias staging
   const int n_tiles = (g.N + BN - 1) / BN;
   const long tiles = static_cast<long>(g.groups) * ((g.M + tc::BM * CG - 1) / (tc::BM * CG)) * n_tiles;
   const int grid = CG * static_cast<int>(std::min<long>(tiles, num_sms() / CG));
@@ -470,23 +481,7 @@ static int launch_tc_cg(const GemmArgs& g, int BN, cudaStream_t st) {
     TNT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBudget + 4096));
     attr_set = true;
   }
-  if (CG == 1) {
-    kern<<<grid, tc::kThreads, smem, st>>>(tmA, tmW, g, BN, stages, n_tiles);
-  } else {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(tc::kThreads);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = CG;
-    at[0].val.clusterDim.y = 1;
-    at[0].val.clusterDim.z = 1;
-    cfg.attrs = at;
-    cfg.numAttrs = 1;
-    TNT_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmW, g, BN, stages, n_tiles));
-  }
+  TNT_CUDA(launch_pdl(kern, dim3(grid), dim3(tc::kThreads), smem, st, CG, tmA, tmW, g, BN, stages, n_tiles));
   TNT_LAUNCHED();
   return TNT_OK;
 }

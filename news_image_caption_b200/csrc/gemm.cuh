@@ -36,18 +36,28 @@ struct LseExtra {
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
 
 // One thread owns NC consecutive accumulator columns [n0, n0+NC) of row m (n0 % NC == 0).
+// `bias_n0` points at the bias of column n0 (or is null); with `bias_padded` it is a zero-padded staging copy
+// (shared memory in the tcgen05 kernel) that may be read NC wide without a bounds check.
 template <int EPI, typename TOut, int NC>
-__device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m, int n0, float (&acc)[NC]) {
+__device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m, int n0, float (&acc)[NC],
+                                               const float* bias_n0, bool bias_padded) {
   static_assert(NC % 8 == 0 || NC == 4, "NC");
-  const float* bias = g.bias ? g.bias + grp * g.sbias : nullptr;
   if (g.alpha != 1.f) {
 #pragma unroll
     for (int i = 0; i < NC; ++i) acc[i] *= g.alpha;
   }
-  if (bias) {
+  if (bias_n0) {
+    if (bias_padded) {
 #pragma unroll
-    for (int i = 0; i < NC; ++i)
-      if (n0 + i < g.N) acc[i] += __ldg(bias + n0 + i);
+      for (int i = 0; i < NC; i += 4) {
+        const float4 b4 = *reinterpret_cast<const float4*>(bias_n0 + i);
+        acc[i] += b4.x; acc[i + 1] += b4.y; acc[i + 2] += b4.z; acc[i + 3] += b4.w;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < NC; ++i)
+        if (n0 + i < g.N) acc[i] += __ldg(bias_n0 + i);
+    }
   }
   TOut* crow = reinterpret_cast<TOut*>(g.c) + grp * g.sc + static_cast<long>(m) * g.ldc;
   if (EPI == EPI_GLU) {
