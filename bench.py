@@ -31,7 +31,7 @@ WORKLOADS = {
     'gen': dict(B=256, sources=('image', 'article'), tag='2src', what='GREEDY generation 32 steps (incremental DynamicConv ring + cached K/V)'),
 }
 # dram bytes (read + write) of one article K/V GEMM launch from the ncu --set full capture in profiles/ (None until captured)
-TRAFFIC_KV_GEMM = None
+TRAFFIC_KV_GEMM = 573.8e6   # profiles/r1_ncu_full_step_B64_pair.txt, id 11: 90.2 MB read + 483.6 MB written
 WORKLOAD = 'tell-decoder-2src L4 d1024 H16 K3/7/15/31 V50265 fwd+adaptive-loss B64/gpu T32 S49+512'
 
 

@@ -184,6 +184,32 @@ typedef struct {
 int tnt_embed_fwd(const tnt_embed_params* p, tnt_stream stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Context assembly in front of the decoder (the model's _forward, between the encoders and the decoder call).
+ *   ttl/tell/models/transformer_faces_objects.py:355-366 : article = sum_l softmax(bert_weight)[l] * hiddens[l]
+ *                                                          over the 25 RoBERTa hidden layers, then .transpose(0,1)
+ *   ttl/tell/models/transformer_faces_objects.py:371-377 : mask = isnan(x).any(-1); x[mask] = 0  (faces, objects)
+ * Outputs are written in the decoder's layout [S, B, E] (the reference's .transpose(0, 1)) and dtype.
+ * ------------------------------------------------------------------------------------------ */
+#define TNT_MAX_MIX_LAYERS 32
+typedef struct {
+  const void* layers[TNT_MAX_MIX_LAYERS]; /* n_layers tensors [B, S, E], contiguous, 32-byte aligned */
+  const float* weight_logits;             /* [n_layers] fp32 (bert_weight, BEFORE the softmax) */
+  void* out;                              /* [S, B, E] */
+  int n_layers, B, S, E;
+  int dtype_in, dtype_out;
+} tnt_context_mix_params;
+int tnt_context_mix(const tnt_context_mix_params* p, tnt_stream stream);
+
+typedef struct {
+  const void* x;        /* [B, n, d] embeddings, NaN rows = padding */
+  void* out;            /* [n, B, d] NaN rows zeroed */
+  uint8_t* mask;        /* [B, n] 1 = padding */
+  int B, n, d;
+  int dtype_in, dtype_out;
+} tnt_nan_mask_params;
+int tnt_nan_mask(const tnt_nan_mask_params* p, tnt_stream stream);
+
+/* ------------------------------------------------------------------------------------------
  * Multi-head cross attention over one or more memory sources.
  *   ttl/tell/modules/attention/multi_head.py:288-486 (manual path, static_kv)
  *   final_roberta2/transformer_v2.py:213-266        (attention(), MultiHeadedAttention)

@@ -58,6 +58,16 @@ class EmbedParams(C.Structure):
                 ('B', i32), ('T', i32), ('d', i32), ('n_pos', i32), ('pad_idx', i32), ('dtype', i32)]
 
 
+class ContextMixParams(C.Structure):
+    _fields_ = [('layers', vp * 32), ('weight_logits', vp), ('out', vp), ('n_layers', i32), ('B', i32), ('S', i32),
+                ('E', i32), ('dtype_in', i32), ('dtype_out', i32)]
+
+
+class NanMaskParams(C.Structure):
+    _fields_ = [('x', vp), ('out', vp), ('mask', vp), ('B', i32), ('n', i32), ('d', i32), ('dtype_in', i32),
+                ('dtype_out', i32)]
+
+
 class XattnParams(C.Structure):
     _fields_ = [('q', vp), ('q_stride_t', i64), ('q_stride_b', i64), ('k', vp), ('k_stride_s', i64),
                 ('k_stride_b', i64), ('v', vp), ('v_stride_s', i64), ('v_stride_b', i64), ('out', vp),
@@ -113,6 +123,8 @@ _SIGS = {
     'tnt_layernorm_fwd': (i32, [C.POINTER(LayernormParams), vp]),
     'tnt_layernorm_bwd': (i32, [C.POINTER(LayernormBwdParams), vp]),
     'tnt_embed_fwd': (i32, [C.POINTER(EmbedParams), vp]),
+    'tnt_context_mix': (i32, [C.POINTER(ContextMixParams), vp]),
+    'tnt_nan_mask': (i32, [C.POINTER(NanMaskParams), vp]),
     'tnt_xattn_fwd': (i32, [C.POINTER(XattnParams), vp]),
     'tnt_xattn_bwd_scratch_bytes': (C.c_size_t, [i32, i32, i32, i32]),
     'tnt_xattn_bwd': (i32, [C.POINTER(XattnBwdParams), vp]),
@@ -144,6 +156,7 @@ _SIGS = {
     'tnt_debug_force_simt_gemm': (None, [i32]),
     'tnt_debug_gemm_cta_group': (None, [i32]),
     'tnt_debug_pdl': (None, [i32]),
+    'tnt_debug_gemm_tile_n': (None, [i32]),
     'tnt_debug_force_simt_attention': (None, [i32]),
     'tnt_debug_force_simt_attention_bwd': (None, [i32]),
 }

@@ -31,6 +31,36 @@ __device__ __forceinline__ void warp_softmax_taps(const T* lg, int K, float* out
   for (int j = lane; j < K; j += 32) out[j] *= inv;
 }
 
+// Tap soft-max of a whole CTA tile in two passes with ONE global-memory latency: every thread copies raw logits
+// (rows x hg*K values, contiguous per row) into taps[(r*HG + hl)*K + j], then one thread per (row, head) normalises
+// its K values in place.  Rows at or beyond `T_end` are zero filled.  Caller syncs before and after phase 2.
+template <typename T>
+__device__ __forceinline__ void stage_tap_logits(const T* lg, long ldl, int B, int b, int t0, int T_end, int rows, int hg,
+                                                 int HG, int K, int h0, float* taps) {
+  const int per_row = hg * K;
+  for (int i = threadIdx.x; i < rows * per_row; i += kThreads) {
+    const int r = i / per_row, rem = i - r * per_row;
+    taps[r * HG * K + rem] = (t0 + r < T_end) ? to_f(lg[(static_cast<long>(t0 + r) * B + b) * ldl + h0 * K + rem]) : 0.f;
+  }
+}
+__device__ __forceinline__ void normalise_taps(int t0, int T_end, int rows, int hg, int HG, int K, float* taps) {
+  for (int i = threadIdx.x; i < rows * hg; i += kThreads) {
+    const int r = i / hg, hl = i - r * hg;
+    if (t0 + r >= T_end) continue;
+    float* o = taps + (r * HG + hl) * K;
+    float m = -INFINITY;
+    for (int j = 0; j < K; ++j) m = fmaxf(m, o[j]);
+    float s = 0.f;
+    for (int j = 0; j < K; ++j) {
+      const float e = __expf(o[j] - m);
+      o[j] = e;
+      s += e;
+    }
+    const float inv = 1.f / s;
+    for (int j = 0; j < K; ++j) o[j] *= inv;
+  }
+}
+
 // ------------------------------------------------------------------------------ forward
 // smem: xs [(TT+K-1)][CC] fp32, taps [TT][HG][K] fp32
 template <typename T>
@@ -49,7 +79,6 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_param
   T* y = reinterpret_cast<T*>(p.y);
   const int cc = min(CC, p.C - c0);
   const int nv = cc >> 3;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   // stage the input window (zeros / history before t = 0)
   for (int i = threadIdx.x; i < rows * nv; i += kThreads) {
@@ -68,13 +97,11 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_param
     *reinterpret_cast<float4*>(d) = make_float4(v[0], v[1], v[2], v[3]);
     *reinterpret_cast<float4*>(d + 4) = make_float4(v[4], v[5], v[6], v[7]);
   }
-  // taps
+  // taps: raw logits -> smem together with the input window (one memory latency), then normalised in place
   const int hg = cc / R, h0 = c0 / R;
-  for (int i = warp; i < TT * hg; i += kThreads / 32) {
-    const int t = i / hg, hl = i - t * hg;
-    warp_softmax_taps(lg + (static_cast<long>(t0 + t) * B + b) * p.ldl + (h0 + hl) * K, K,
-                      taps + (t * HG + hl) * K, lane);
-  }
+  stage_tap_logits(lg, p.ldl, B, b, t0, p.T, TT, hg, HG, K, h0, taps);
+  __syncthreads();
+  normalise_taps(t0, p.T, TT, hg, HG, K, taps);
   __syncthreads();
   for (int i = threadIdx.x; i < TT * nv; i += kThreads) {
     const int t = i / nv, vc = i - t * nv;
@@ -174,15 +201,9 @@ __global__ void __launch_bounds__(kThreads) dynconv_bwd_kernel(tnt_dynconv_bwd_p
 #pragma unroll
     for (int j = 0; j < 8; ++j) dys[r * CCP + vc * 8 + j] = v[j];
   }
-  for (int i = warp; i < rows * hg; i += kThreads / 32) {
-    const int r = i / hg, hl = i - r * hg;
-    float* o = taps + (r * HG + hl) * K;
-    if (t0 + r < p.T) {
-      warp_softmax_taps(lg + (static_cast<long>(t0 + r) * B + b) * p.ldl + (h0 + hl) * K, K, o, lane);
-    } else {
-      for (int j = lane; j < K; j += 32) o[j] = 0.f;
-    }
-  }
+  stage_tap_logits(lg, p.ldl, B, b, t0, p.T, rows, hg, HG, K, h0, taps);
+  __syncthreads();
+  normalise_taps(t0, p.T, rows, hg, HG, K, taps);
   __syncthreads();
 
   // dx[ts] = sum_j w[ts+KM-j][j] * dy[ts+KM-j]   (value path)

@@ -425,11 +425,18 @@ int make_tmap_bf16_3d(CUtensorMap* tm, const void* base, long d0, long d1, long 
 }
 
 static int g_cta_group = 0;   // test hook: 0 = automatic, 1 / 2 = force the single-CTA / CTA-pair kernel
+static int g_force_bn = 0;    // tuning hook: force the tile width (32..256; CTA pair: 64..256)
 
 // tile shape the tcgen05 dispatcher uses: CTA-pair 256 x 256 tiles when the problem fills the 74 SM pairs for
 // several waves, else single-CTA 128 x BN with BN shrunk until the grid covers the SMs
 static void pick_tile(int M, int N, int groups, bool b_mn, int* bn_out, int* cg_out) {
   const int sms = num_sms();
+  if (g_force_bn) {
+    *cg_out = g_cta_group == 2 ? 2 : 1;
+    *bn_out = g_force_bn;
+    if (b_mn && *bn_out / *cg_out < 64) *bn_out = 64 * *cg_out;
+    return;
+  }
   if (g_cta_group != 1 && M >= 256 && N >= 256) {
     const long pair_tiles = static_cast<long>(groups) * ((M + 255) / 256) * ((N + 255) / 256);
     if (g_cta_group == 2 || pair_tiles >= 4L * (sms / 2)) {
@@ -446,7 +453,9 @@ static void pick_tile(int M, int N, int groups, bool b_mn, int* bn_out, int* cg_
     const int bn = cands[i];
     if (i < last && N <= cands[i + 1]) continue;       // tile would be mostly padding
     const long tiles = static_cast<long>(groups) * m_tiles * ((N + bn - 1) / bn);
-    if (tiles >= sms || i == last) {
+    // measured (tools/tune_gemm.py, profiles/r1_gemm_tile_sweep.txt): the widest tile that still gives ~3/4 of the SMs a
+    // tile wins -- narrower tiles re-read the 128-row A block once per n tile and become L2->SM bound
+    if (tiles * 4 >= 3L * sms || i == last) {
       *bn_out = bn;
       return;
     }
@@ -585,3 +594,4 @@ extern "C" int tnt_linear_fwd(const tnt_linear_params* p, tnt_stream stream) {
 }
 extern "C" void tnt_debug_force_simt_gemm(int on) { tnt::gemm_force_simt(on != 0); }
 extern "C" void tnt_debug_gemm_cta_group(int cg) { tnt::g_cta_group = (cg == 1 || cg == 2) ? cg : 0; }
+extern "C" void tnt_debug_gemm_tile_n(int bn) { tnt::g_force_bn = (bn == 32 || bn == 64 || bn == 128 || bn == 256) ? bn : 0; }

@@ -274,3 +274,36 @@ def lse(x, w, bias=None, target=None):
     p.M, p.n_cols, p.K, p.dtype = M, N, K, _code(x)
     _lib.check(L.tnt_lse_fwd(C.byref(p), _st()), 'tnt_lse_fwd')
     return stats[:, 0], stats[:, 1], stats[:, 2].contiguous().view(torch.int32), stats[:, 3]
+
+
+def context_mix(hiddens, weight_logits, out_dtype=None):
+    """transformer_faces_objects.py:355-366: sum_l softmax(bert_weight)[l] * hiddens[l], transposed.
+    hiddens: list of [B,S,E] CUDA tensors (same dtype) -> [S,B,E]."""
+    hs = [_cuda(h).contiguous() for h in hiddens]
+    B, S, E = hs[0].shape
+    out_dtype = out_dtype or hs[0].dtype
+    out = torch.empty(S, B, E, dtype=out_dtype, device=hs[0].device)
+    wl = weight_logits.to(hs[0].device, torch.float32).contiguous()
+    p = _lib.ContextMixParams()
+    for i, h in enumerate(hs):
+        if h.shape != hs[0].shape or h.dtype != hs[0].dtype:
+            raise ValueError('context_mix: hidden %d differs in shape / dtype' % i)
+        p.layers[i] = h.data_ptr()
+    p.weight_logits, p.out = wl.data_ptr(), out.data_ptr()
+    p.n_layers, p.B, p.S, p.E = len(hs), B, S, E
+    p.dtype_in, p.dtype_out = _code(hs[0]), _code(out)
+    _lib.check(_lib.lib().tnt_context_mix(C.byref(p), _st()), 'tnt_context_mix')
+    return out
+
+
+def nan_mask(x, out_dtype=None):
+    """transformer_faces_objects.py:371-377: ([n,B,d] with NaN rows zeroed, mask [B,n] bool True = padding)."""
+    x = _cuda(x).contiguous()
+    B, n, d = x.shape
+    out = torch.empty(n, B, d, dtype=out_dtype or x.dtype, device=x.device)
+    mask = torch.empty(B, n, dtype=torch.bool, device=x.device)
+    p = _lib.NanMaskParams()
+    p.x, p.out, p.mask, p.B, p.n, p.d = x.data_ptr(), out.data_ptr(), mask.data_ptr(), B, n, d
+    p.dtype_in, p.dtype_out = _code(x), _code(out)
+    _lib.check(_lib.lib().tnt_nan_mask(C.byref(p), _st()), 'tnt_nan_mask')
+    return out, mask

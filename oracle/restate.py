@@ -339,6 +339,24 @@ def greedy_generate(seed_ids: torch.Tensor, contexts: dict, sd: SD, H: int,
     return torch.cat(lps, 1), torch.cat(toks, 1)
 
 
+# ----------------------------------------------------------------------------- context assembly
+def context_mix(hiddens: Sequence[torch.Tensor], bert_weight: torch.Tensor) -> torch.Tensor:
+    """RoBERTa hidden-layer mix -- ttl/tell/models/transformer_faces_objects.py:355-366 (weigh_bert) and the
+    `.transpose(0, 1)` of :383.  hiddens: n tensors [B,S,E]; bert_weight [n] -> [S,B,E]."""
+    X = torch.stack(list(hiddens), dim=2)
+    w = F.softmax(bert_weight, dim=0).unsqueeze(0).unsqueeze(1).unsqueeze(3)
+    return (X * w).sum(dim=2).transpose(0, 1)
+
+
+def nan_padding_mask(embeds: torch.Tensor):
+    """faces / objects: NaN rows are padding -- ttl/tell/models/transformer_faces_objects.py:371-377 (+ :388,390).
+    embeds [B,n,d] -> ([n,B,d] with padding rows zeroed, mask [B,n] True = padding)."""
+    m = torch.isnan(embeds).any(dim=-1)
+    e = embeds.clone()
+    e[m] = 0
+    return e.transpose(0, 1), m
+
+
 # ----------------------------------------------------------------------------- final*/transformer_v2
 def v2_layer_norm(x, a, b, eps=1e-6):
     """final*/transformer_v2.py:82-94: UNBIASED std, eps added to the std (outside the sqrt)."""

@@ -356,3 +356,32 @@ def test_lse(ops, dtype):
     assert rel_err(tz, z.gather(1, tgt[:, None])[:, 0]) < (1e-5 if dtype == torch.float32 else 1e-2)
     if dtype == torch.float32:
         assert torch.equal(arg.cpu().long(), z.argmax(1))
+
+
+# ----------------------------------------------------------------------------- context assembly (row f2)
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize('B,S,E,n', [(3, 17, 1024, 25), (2, 512, 1024, 25), (1, 5, 64, 13), (4, 33, 256, 1)])
+def test_context_mix(ops, dtype, B, S, E, n):
+    g = torch.Generator().manual_seed(B + S + n)
+    hs = [torch.randn(B, S, E, generator=g).to(dtype) for _ in range(n)]
+    w = torch.randn(n, generator=g)
+    ref = O.context_mix([h.float() for h in hs], w)
+    out = ops.context_mix([h.cuda() for h in hs], w)
+    assert out.shape == (S, B, E) and out.dtype == dtype
+    assert rel_err(out, ref) < (1e-5 if dtype == torch.float32 else 8e-3)
+    out32 = ops.context_mix([h.cuda() for h in hs], w, out_dtype=torch.float32)
+    assert rel_err(out32, ref) < 1e-5
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_nan_mask(ops, dtype):
+    g = torch.Generator().manual_seed(4)
+    for B, n, d in ((5, 4, 512), (3, 64, 2048), (2, 1, 40)):
+        x = torch.randn(B, n, d, generator=g).to(dtype)
+        pad = torch.rand(B, n, generator=g) < 0.4
+        x[pad] = float('nan')
+        x[0, 0, d // 2] = float('nan')                       # a single NaN element also marks the row
+        ref, mref = O.nan_padding_mask(x.float())
+        out, m = ops.nan_mask(x.cuda())
+        assert torch.equal(m.cpu(), mref)
+        assert torch.equal(out.float().cpu(), ref)           # pure copy / zero fill: bit exact
