@@ -237,6 +237,8 @@ typedef struct {
   int dtype;
   int mask_S;         /* the mask covers keys [0, mask_S); 0 = all S (trailing k/v rows are then never masked) */
   float* lse;         /* optional [B, H, T] fp32: log-sum-exp of the scaled, masked scores (saved for the backward) */
+  int kv_group;       /* beam search: query rows b*kv_group .. +kv_group-1 share the k / v / mask of batch entry b
+                         (B counts query rows; 0 or 1 = one k / v entry per query row) */
 } tnt_xattn_params;
 int tnt_xattn_fwd(const tnt_xattn_params* p, tnt_stream stream);
 
@@ -342,6 +344,15 @@ int tnt_decoder_log_prob(tnt_decoder* d, const void* X, int n_rows, float* out, 
  * seed [B] first token; ids_out [B, gen_len+1] (col 0 = seed, finished rows padded with pad_idx);
  * logp_out [B, gen_len] (0 after the row finished).  Runs all steps; returns in *steps_host (may be
  * NULL) the number of steps after which every row had finished (host sync only if non-NULL). */
+/* beam-search generation (models/CaptionModel.py:23-122 scoring / candidate order / finished-beam rule; state fork =
+ * reorder_incremental_state, dynamic.py:338-348).  Per caption `beam` (<= 16) hypotheses; the beams share the caption's
+ * cached K/V.  Runs exactly gen_len (<= 128) steps like the reference loop.  Outputs, best first:
+ * seq_out [B, beam, gen_len] (0 after the end of a hypothesis), logp_out [B, beam, gen_len] (per-word log-probs),
+ * p_out [B, beam] (summed log-prob).  ctx->B = number of captions. */
+size_t tnt_decoder_beam_workspace_bytes(const tnt_decoder* d, int B, int beam, int gen_len, const int* S);
+int tnt_decoder_generate_beam(tnt_decoder* d, const int64_t* seed, const tnt_contexts* ctx, int gen_len, int eos, int beam,
+                              int64_t* seq_out, float* logp_out, float* p_out, void* workspace, size_t workspace_bytes,
+                              tnt_stream stream);
 size_t tnt_decoder_generate_workspace_bytes(const tnt_decoder* d, int B, int gen_len, const int* S);
 int tnt_decoder_generate(tnt_decoder* d, const int64_t* seed, const tnt_contexts* ctx, int gen_len, int eos,
                          int64_t* ids_out, float* logp_out, int* steps_host, void* workspace,

@@ -73,7 +73,7 @@ class XattnParams(C.Structure):
                 ('k_stride_b', i64), ('v', vp), ('v_stride_s', i64), ('v_stride_b', i64), ('out', vp),
                 ('o_stride_t', i64), ('o_stride_b', i64), ('mask', vp), ('m_stride_b', i64), ('m_stride_t', i64),
                 ('bias_k', vp), ('bias_v', vp), ('weights', vp), ('B', i32), ('T', i32), ('S', i32), ('H', i32),
-                ('D', i32), ('n_extra', i32), ('mask_mode', i32), ('scale', f32), ('dtype', i32), ('mask_S', i32), ('lse', vp)]
+                ('D', i32), ('n_extra', i32), ('mask_mode', i32), ('scale', f32), ('dtype', i32), ('mask_S', i32), ('lse', vp), ('kv_group', i32)]
 
 
 class XattnBwdParams(C.Structure):
@@ -143,6 +143,8 @@ _SIGS = {
     'tnt_decoder_log_prob': (i32, [vp, vp, i32, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_generate_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
     'tnt_decoder_generate': (i32, [vp, vp, C.POINTER(Contexts), i32, i32, vp, vp, C.POINTER(i32), vp, C.c_size_t, vp]),
+    'tnt_decoder_beam_workspace_bytes': (C.c_size_t, [vp, i32, i32, i32, C.POINTER(i32)]),
+    'tnt_decoder_generate_beam': (i32, [vp, vp, C.POINTER(Contexts), i32, i32, i32, vp, vp, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_score_host_staging_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
     'tnt_decoder_score_host': (i32, [vp, vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp, C.c_size_t, vp]),
     'tnt_decoder_score_host_submit': (i32, [vp, i32, vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp, C.c_size_t, vp]),

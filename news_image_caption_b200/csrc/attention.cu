@@ -19,6 +19,8 @@ struct Smem {
   float* qs; float* ks; float* vs; float* ps;
 };
 
+__device__ __forceinline__ int kv_batch(const tnt_xattn_params& p, int b) { return p.kv_group > 1 ? b / p.kv_group : b; }
+
 template <typename T>
 __device__ __forceinline__ void load_kv_tile(const tnt_xattn_params& p, const T* kp, const T* vp, int b, int h,
                                              int key0, float* ks, float* vs) {
@@ -68,7 +70,7 @@ __device__ __forceinline__ void tile_scores(const tnt_xattn_params& p, const flo
 #pragma unroll
       for (int qi = 0; qi < kQW; ++qi) s[qi][e] = -INFINITY;
     } else if (key < S && p.mask_mode == TNT_MASK_KEY_PADDING) {
-      if (p.mask[static_cast<long>(b) * p.m_stride_b + key]) {
+      if (p.mask[static_cast<long>(kv_batch(p, b)) * p.m_stride_b + key]) {
 #pragma unroll
         for (int qi = 0; qi < kQW; ++qi) s[qi][e] = -INFINITY;
       }
@@ -128,7 +130,7 @@ __global__ void __launch_bounds__(kThreads) xattn_fwd_kernel(tnt_xattn_params p)
 
   for (int key0 = 0; key0 < S2; key0 += kTK) {
     __syncthreads();
-    load_kv_tile<T>(p, kp, vp, b, h, key0, ks, vs);
+    load_kv_tile<T>(p, kp, vp, kv_batch(p, b), h, key0, ks, vs);
     __syncthreads();
     if (nq == 0) continue;
     float s[kQW][2];
@@ -181,7 +183,7 @@ __global__ void __launch_bounds__(kThreads) xattn_fwd_kernel(tnt_xattn_params p)
     const float invH = 1.f / p.H;
     for (int key0 = 0; key0 < S2; key0 += kTK) {
       __syncthreads();
-      load_kv_tile<T>(p, kp, vp, b, h, key0, ks, vs);
+      load_kv_tile<T>(p, kp, vp, kv_batch(p, b), h, key0, ks, vs);
       __syncthreads();
       if (nq == 0) continue;
       float s[kQW][2];

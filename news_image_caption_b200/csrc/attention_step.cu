@@ -47,11 +47,12 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(tnt_xattn_param
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int h = hg * kHeadsPerCta + (lane >> 2), d0 = (lane & 3) * 16;
   const bf16* qp = reinterpret_cast<const bf16*>(p.q) + static_cast<long>(b) * p.q_stride_b + h * 64 + d0;
-  const bf16* kp = reinterpret_cast<const bf16*>(p.k) + static_cast<long>(b) * p.k_stride_b + h * 64 + d0;
-  const bf16* vp = reinterpret_cast<const bf16*>(p.v) + static_cast<long>(b) * p.v_stride_b + h * 64 + d0;
+  const int bk = p.kv_group > 1 ? b / p.kv_group : b;     // beams of one caption share its K / V / mask
+  const bf16* kp = reinterpret_cast<const bf16*>(p.k) + static_cast<long>(bk) * p.k_stride_b + h * 64 + d0;
+  const bf16* vp = reinterpret_cast<const bf16*>(p.v) + static_cast<long>(bk) * p.v_stride_b + h * 64 + d0;
   const int S = p.S;
   const int SM = p.mask_mode == TNT_MASK_KEY_PADDING ? (p.mask_S > 0 ? min(p.mask_S, S) : S) : 0;   // keys the mask covers
-  const uint8_t* mrow = p.mask + static_cast<long>(b) * p.m_stride_b;
+  const uint8_t* mrow = p.mask + static_cast<long>(bk) * p.m_stride_b;
 
   float q[16];
   {

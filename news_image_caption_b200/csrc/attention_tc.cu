@@ -309,7 +309,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 }  // namespace atc
 
 bool xattn_tc_supported(const tnt_xattn_params* p) {
-  if (p->dtype != TNT_BF16 || p->D != 64 || (p->H & 1) || p->n_extra != 0 || p->weights) return false;
+  if (p->dtype != TNT_BF16 || p->D != 64 || (p->H & 1) || p->n_extra != 0 || p->weights || p->kv_group > 1) return false;
   if (p->mask_mode != TNT_MASK_NONE && p->mask_mode != TNT_MASK_KEY_PADDING) return false;
   if (p->S < 1 || p->S > atc::MAX_TILES * atc::TKEYS) return false;
   const long strides = p->q_stride_t | p->q_stride_b | p->k_stride_s | p->k_stride_b | p->v_stride_s | p->v_stride_b;

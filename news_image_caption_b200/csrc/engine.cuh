@@ -84,12 +84,14 @@ struct FwdWs {
   float* lse[TNT_MAX_SOURCES];   // training: attention log-sum-exp [B, H, T] per source (NULL: not saved)
   size_t total;
 };
-FwdWs carve_fwd(const tnt_decoder* d, int B, int T, const int* S, void* ws, bool with_kv);
+// B_kv >= 0: number of context entries the K/V cache holds when it differs from the row batch B (beam search)
+FwdWs carve_fwd(const tnt_decoder* d, int B, int T, const int* S, void* ws, bool with_kv, int B_kv = -1);
 
 int embed(tnt_decoder* d, const int64_t* ids, int B, int T, void* out, const int* start_pos, cudaStream_t st);
 int project_kv(tnt_decoder* d, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st);
 // one decoder layer on N = T*B rows; `ring`/`pos` != NULL selects the single-step conv (T must be 1)
 int run_layer(tnt_decoder* d, int l, const tnt_contexts* ctx, const FwdWs& w, const void* Xin, void* Xout, int B, int T,
-              void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st);
+              void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st, int kv_group = 1);
+// kv_group > 1 (beam search): B counts beam rows; rows b*kv_group.. share context entry b (ctx->B = B / kv_group)
 
 }  // namespace tnt

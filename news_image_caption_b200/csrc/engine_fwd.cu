@@ -45,7 +45,7 @@ __global__ void kv_extra_rows_kernel(T* kv, const float* row, int S, int B, int 
 }
 }  // namespace
 
-FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool with_kv) {
+FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool with_kv, int B_kv) {
   const tnt_decoder_config& c = D->cfg;
   const size_t E = D->esz(), N = static_cast<size_t>(B) * T, d = c.d, ns = c.n_sources;
   size_t off = 0;
@@ -63,7 +63,7 @@ FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool
   w.ybuf2 = w.ybuf;
   w.CATln = w.CAT;
   for (size_t s = 0; s < ns; ++s)
-    w.kv[s] = with_kv ? take(static_cast<size_t>(S[s] + 2) * B * c.n_layers * 2 * d * E) : nullptr;
+    w.kv[s] = with_kv ? take(static_cast<size_t>(S[s] + 2) * (B_kv >= 0 ? B_kv : B) * c.n_layers * 2 * d * E) : nullptr;
   w.total = off;
   return w;
 }
@@ -94,7 +94,7 @@ int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStre
 }
 
 int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, const void* Xin, void* Xout, int B, int T,
-              void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st) {
+              void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st, int kv_group) {
   const tnt_decoder_config& c = D->cfg;
   const LayerW& L = D->layers[l];
   const int d = c.d, ns = c.n_sources, N = B * T, H = c.heads, dt = c.dtype;
@@ -125,7 +125,7 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     ap.q = static_cast<const char*>(w.Q) + static_cast<size_t>(s) * d * E;
     ap.q_stride_t = static_cast<long>(B) * ns * d; ap.q_stride_b = static_cast<long>(ns) * d;
     ap.k = static_cast<const char*>(w.kv[s]) + static_cast<size_t>(l) * 2 * d * E;
-    ap.k_stride_s = static_cast<long>(B) * ldkv; ap.k_stride_b = ldkv;
+    ap.k_stride_s = static_cast<long>(B / (kv_group > 1 ? kv_group : 1)) * ldkv; ap.k_stride_b = ldkv;   // cache rows = context entries
     ap.v = static_cast<const char*>(ap.k) + static_cast<size_t>(d) * E;
     ap.v_stride_s = ap.k_stride_s; ap.v_stride_b = ap.k_stride_b;
     ap.out = static_cast<char*>(w.AO) + static_cast<size_t>(s) * d * E;
@@ -137,6 +137,7 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     // the K/V buffer carries the 2 extra rows (project_kv), so they are plain keys the mask does not cover
     ap.B = B; ap.T = T; ap.S = ctx->S[s] + 2; ap.H = H; ap.D = d / H; ap.n_extra = 0;
     ap.mask_S = ctx->S[s];
+    ap.kv_group = kv_group;
     if (ctx->S[s] == 0) ap.mask_mode = TNT_MASK_NONE;
     ap.scale = 1.0f / sqrtf(static_cast<float>(d / H));
     ap.dtype = dt;

@@ -289,6 +289,29 @@ class DynamicConvDecoder(nn.Module):
             return lp[:, :n], ids[:, :n + 1]
         return lp, ids
 
+    def generate_beam(self, seed, contexts, gen_len=20, beam_size=5, eos=2):
+        """Beam search with the scoring / bookkeeping of `CaptionModel.beam_search` (models/CaptionModel.py:23-122)
+        over the incremental decoder; `reorder_incremental_state` happens on the device.  Returns, best first:
+        (seq [B, beam, gen_len] -- 0 after a hypothesis ended, logps [B, beam, gen_len], p [B, beam])."""
+        seed = seed.to('cuda', torch.long)
+        if seed.dim() == 2:
+            seed = seed[:, -1]
+        seed = seed.contiguous()
+        B = seed.shape[0]
+        L, h = _lib.lib(), self._h()
+        ctx, keep = self._contexts(contexts, B, 1)
+        S = (C.c_int * 4)(*[ctx.S[i] for i in range(4)])
+        nbytes = L.tnt_decoder_beam_workspace_bytes(h, B, beam_size, gen_len, S)
+        if nbytes == 0:
+            raise ValueError('generate_beam: beam_size must be in [1, 16] and gen_len in [1, 128]')
+        ws = self._workspace('beam', nbytes)
+        seq = torch.empty(B, beam_size, gen_len, dtype=torch.long, device='cuda')
+        lps = torch.empty(B, beam_size, gen_len, dtype=torch.float32, device='cuda')
+        p = torch.empty(B, beam_size, dtype=torch.float32, device='cuda')
+        _lib.check(L.tnt_decoder_generate_beam(h, _ptr(seed), C.byref(ctx), gen_len, eos, beam_size, _ptr(seq), _ptr(lps),
+                                               _ptr(p), _ptr(ws), ws.numel(), _stream()), 'tnt_decoder_generate_beam')
+        return seq, lps, p
+
     # ------------------------------------------------------------------ training (kernel group 4)
     def tied_keys(self):
         """Output-softmax rows tied to the embedding bands (softmax.py:83-86,111-132): alias -> owner."""

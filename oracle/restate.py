@@ -339,6 +339,82 @@ def greedy_generate(seed_ids: torch.Tensor, contexts: dict, sd: SD, H: int,
     return torch.cat(lps, 1), torch.cat(toks, 1)
 
 
+# ----------------------------------------------------------------------------- beam search
+def beam_search(step_fn, reorder_fn, beam_size: int, seq_length: int, eos: int, return_all: bool = False):
+    """`CaptionModel.beam_search` -- models/CaptionModel.py:23-122, restated for ONE caption.
+    step_fn(tokens [W] or None for the seed step) -> log-probs [W, V] of the next word for every beam;
+    reorder_fn(order [W]) forks the recurrent state (new beam vix continues old beam order[vix]; the reference
+    copies `state[:, q]`, for the tell decoder this is `reorder_incremental_state`).  `eos` is the end token (0 there).
+    Returns the list of finished beams sorted by score, at most beam_size: dicts seq [L], logps [L], p
+    (`return_all`: every finished beam in arrival order, unsorted).
+    Quirk of the reference under torch >= 0.4: `'p': beam_logprobs_sum[vix]` stores a 0-dim VIEW, which the next line
+    (`beam_logprobs_sum[vix] = -1000`) overwrites, so its final sort sees equal keys and keeps arrival order; the score
+    the code means (the value at finishing time, what old torch returned as a Python float) is what is restated here."""
+    W, L = beam_size, seq_length
+    beam_seq = torch.zeros(L, W, dtype=torch.long)
+    beam_seq_logprobs = torch.zeros(L, W)
+    beam_logprobs_sum = torch.zeros(W)
+    done_beams = []
+    logprobs = step_fn(None)
+    for t in range(L):
+        logprobsf = logprobs.float()
+        ys, ix = torch.sort(logprobsf, 1, True)                      # :41
+        candidates = []
+        cols = min(W, ys.size(1))
+        rows = 1 if t == 0 else W                                    # :44-46
+        for c in range(cols):
+            for q in range(rows):
+                local = ys[q, c]
+                candidates.append({'c': ix[q, c], 'q': q, 'p': beam_logprobs_sum[q] + local, 'r': local})
+        candidates = sorted(candidates, key=lambda x: -x['p'])       # stable, :53
+        if t >= 1:
+            seq_prev = beam_seq[:t].clone()
+            lp_prev = beam_seq_logprobs[:t].clone()
+        order = []
+        for vix in range(W):
+            v = candidates[vix]
+            if t >= 1:
+                beam_seq[:t, vix] = seq_prev[:, v['q']]
+                beam_seq_logprobs[:t, vix] = lp_prev[:, v['q']]
+            order.append(v['q'])
+            beam_seq[t, vix] = v['c']
+            beam_seq_logprobs[t, vix] = v['r']
+            beam_logprobs_sum[vix] = v['p']
+        reorder_fn(torch.tensor(order))
+        for vix in range(W):                                         # :102-112
+            if beam_seq[t, vix] == eos or t == L - 1:
+                done_beams.append({'seq': beam_seq[:, vix].clone(), 'logps': beam_seq_logprobs[:, vix].clone(),
+                                   'p': beam_logprobs_sum[vix].clone()})
+                beam_logprobs_sum[vix] = -1000
+        logprobs = step_fn(beam_seq[t])
+    if return_all:
+        return done_beams
+    return sorted(done_beams, key=lambda x: -x['p'])[:W]
+
+
+def decoder_beam_search(seed_id: int, contexts: dict, sd: SD, H: int, cutoffs: Sequence[int], sources, beam_size: int,
+                        gen_len: int, eos: int = 2):
+    """Beam search of ONE caption over the incremental tell decoder: contexts hold that caption only ([S,1,dim]);
+    the W beams form the batch.  State fork = reorder_incremental_state (dynamic.py:338-348): index_select(1, order)
+    on every conv input buffer."""
+    W = beam_size
+    ctx = {k: (v.expand(v.shape[0], W, v.shape[2]) if v.dim() == 3 else v.expand(W, v.shape[1])) for k, v in contexts.items()
+           if v is not None}
+    state: dict = {}
+
+    def step(tokens):
+        cur = torch.full((W, 1), seed_id, dtype=torch.long) if tokens is None else tokens.view(W, 1)
+        X, _ = decoder_forward(cur, ctx, sd, H, cutoffs, sources, state)
+        return adaptive_log_prob(X[:, -1:], sd, cutoffs)[:, 0]
+
+    def reorder(order):
+        for k, v in state.items():
+            if isinstance(k, tuple) and k[0] == 'conv' and v[0] is not None:
+                v[0] = v[0].index_select(1, order)
+
+    return beam_search(step, reorder, W, gen_len, eos)
+
+
 # ----------------------------------------------------------------------------- context assembly
 def context_mix(hiddens: Sequence[torch.Tensor], bert_weight: torch.Tensor) -> torch.Tensor:
     """RoBERTa hidden-layer mix -- ttl/tell/models/transformer_faces_objects.py:355-366 (weigh_bert) and the

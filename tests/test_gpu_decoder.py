@@ -165,3 +165,57 @@ def test_loss_properties_full_vocab(full_model):
             exp -= lpc.view(-1, 50265)[r, t].item()
     assert abs(out[0].item() - exp) < 1e-4 * abs(exp)
     assert int(out[1].item()) == int((tgt != 1).sum())
+
+
+# ----------------------------------------------------------------------------- beam search (row f1)
+def _oracle_beams(prev, ctx, sd, cfg, W, L, eos):
+    out = []
+    for b in range(prev.shape[0]):
+        cb = {k: (v[:, b:b + 1] if v.dim() == 3 else v[b:b + 1]) for k, v in ctx.items()}
+        out.append(O.decoder_beam_search(int(prev[b, 0]), cb, sd, cfg['heads'], cfg['cutoffs'], cfg['sources'], W, L, eos))
+    return out
+
+
+def _check_beams(seq, lps, p, ref, tol):
+    for b, beams in enumerate(ref):
+        assert len(beams) == seq.shape[1]
+        for j, bm in enumerate(beams):
+            assert torch.equal(seq[b, j].cpu(), bm['seq']), (b, j, seq[b, j].cpu(), bm['seq'])
+            assert (lps[b, j].cpu() - bm['logps']).abs().max().item() < tol
+            assert abs(p[b, j].item() - float(bm['p'])) < tol * max(1.0, abs(float(bm['p'])))
+
+
+@pytest.mark.parametrize('name', ['tell2_small.pt', 'tell4_small.pt'])
+@pytest.mark.parametrize('W,L', [(3, 6), (1, 4), (5, 9)])
+def test_beam_search_golden_models_fp32(name, W, L):
+    """Device beam search (shared K/V across beams, ring buffers forked on the device, CUDA-graph steps) vs the oracle
+    (pinned against the reference's CaptionModel.beam_search) on the golden fixture models: hypotheses bit-exact in
+    fp32, per-word log-probs and scores 1e-4.  eos is taken from the greedy fixture so that some beams end early."""
+    f = torch.load(os.path.join(G, name), weights_only=False)
+    cfg, sd = f['config'], f['state_dict']
+    dec = make_decoder(cfg, sd, torch.float32)
+    prev = f['prev'][:, :1]
+    eos = int(f['greedy_ids'][0, min(3, f['greedy_ids'].shape[1] - 1)])     # a token the model likes: early finishes
+    ref = _oracle_beams(prev, f['contexts'], sd, cfg, W, L, eos)
+    seq, lps, p = dec.generate_beam(prev.cuda(), cuda_ctx(f['contexts']), gen_len=L, beam_size=W, eos=eos)
+    _check_beams(seq, lps, p, ref, 1e-4)
+
+
+def test_beam_search_full_size(full_model):
+    cfg, sd = full_model
+    prev, tgt, ctx = synth.make_batch(2, 32, 50265, ('image', 'article'), seed=5)
+    W, L = 3, 4
+    ref = _oracle_beams(prev[:, :1], ctx, sd, cfg, W, L, 2)
+    dec = make_decoder(cfg, sd, torch.float32)
+    seq, lps, p = dec.generate_beam(prev[:, :1].cuda(), cuda_ctx(ctx), gen_len=L, beam_size=W, eos=2)
+    _check_beams(seq, lps, p, ref, 1e-4)
+    # bf16 (decode-step attention kernel with kv_group): scores ordered, p == sum of the word log-probs, and beam 1 of
+    # width 1 == greedy
+    dec16 = make_decoder(cfg, sd, torch.bfloat16)
+    seq, lps, p = dec16.generate_beam(prev[:, :1].cuda(), cuda_ctx(ctx), gen_len=6, beam_size=4, eos=-1)
+    assert bool((p[:, :-1] >= p[:, 1:]).all())
+    assert (lps.sum(-1) - p).abs().max().item() < 1e-3
+    s1, l1, p1 = dec16.generate_beam(prev[:, :1].cuda(), cuda_ctx(ctx), gen_len=6, beam_size=1, eos=-1)
+    lp_g, ids_g = dec16.generate(prev[:, :1].cuda(), cuda_ctx(ctx), gen_len=6, eos=-1, trim=False)
+    assert torch.equal(s1[:, 0], ids_g[:, 1:])
+    assert (l1[:, 0] - lp_g).abs().max().item() < 2e-2

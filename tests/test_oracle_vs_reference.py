@@ -1,5 +1,6 @@
 """CPU, build container only: the oracle against the UNMODIFIED reference modules imported from
 /root/reference at fresh seeds / shapes the fixtures do not cover (skipped on the GPU box)."""
+import os
 import warnings
 
 import pytest
@@ -93,3 +94,78 @@ def test_v2_other_variant():
     sd = {k: v for k, v in m.state_dict().items()}
     close(O.v2_decode(ids, mem, tv.subsequent_mask(5), sd, 4), out)
     torch.set_grad_enabled(True)
+
+
+# ----------------------------------------------------------------------------- beam search (row f1)
+def _reference_caption_model():
+    """The UNMODIFIED models/CaptionModel.py of the reference (its only non-torch import, misc.utils, is unused by
+    beam_search and stubbed)."""
+    import importlib.util
+    import sys
+    import types
+    for name in ('misc', 'misc.utils'):
+        sys.modules.setdefault(name, types.ModuleType(name))
+    path = os.path.join(ri.REF_ROOT, 'models', 'CaptionModel.py')
+    spec = importlib.util.spec_from_file_location('ref_caption_model', path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.CaptionModel
+
+
+@pytest.mark.parametrize('seed,eos_bias', [(0, -30.0), (1, 0.0), (2, 1.5), (3, 3.0)])
+def test_beam_search_matches_reference(monkeypatch, seed, eos_bias):
+    """oracle.beam_search vs the reference's CaptionModel.beam_search on a small recurrent toy model (the search logic
+    is model-agnostic).  End token 0 as in the reference.  The reference's final sort is blind under torch >= 0.4
+    (its stored score is a view that the next line overwrites, see the oracle docstring), so it returns the first
+    `beam` finished beams in ARRIVAL order: that list must equal the head of the oracle's arrival-order list; with
+    no early end token (eos_bias = -30) arrival order == score order and the sorted outputs must agree too."""
+    CaptionModel = _reference_caption_model()
+    monkeypatch.setattr(torch.Tensor, 'cuda', lambda self, *a, **k: self)
+    g = torch.Generator().manual_seed(seed)
+    V, Hd, W, L = 23, 16, 4, 7
+    emb = torch.randn(V, Hd, generator=g)
+    Wh = torch.randn(Hd, Hd, generator=g) * 0.5
+    Wo = torch.randn(V, Hd, generator=g)
+    bias = torch.zeros(V)
+    bias[0] = eos_bias
+
+    def cell(it, h):                                   # h [1, W, Hd]: "dimension one is the beam" as in the reference
+        h2 = torch.tanh(emb[it][None] + h @ Wh)
+        return torch.log_softmax(h2[0] @ Wo.t() + bias, -1), h2
+
+    class Toy(CaptionModel):
+        seq_length = L
+
+        def get_logprobs_state(self, it, state):
+            lp, h2 = cell(it, state[0])
+            return lp, [h2]
+
+    h0 = torch.zeros(1, W, Hd)
+    lp0, h1 = cell(torch.full((W,), 5), h0)
+    ref = Toy().beam_search([h1.clone()], lp0.clone(), opt={'beam_size': W})
+
+    st = {'h': h0.clone()}
+
+    def step(tokens):
+        it = torch.full((W,), 5) if tokens is None else tokens
+        lp, st['h'] = cell(it, st['h'])
+        return lp
+
+    def reorder(order):
+        st['h'] = st['h'].index_select(1, order)
+
+    mine_all = O.beam_search(step, reorder, W, L, eos=0, return_all=True)
+    assert len(ref) == W and len(mine_all) >= W
+    for r, m in zip(ref, mine_all[:W]):
+        assert torch.equal(r['seq'], m['seq'])
+        assert torch.allclose(r['logps'], m['logps'], atol=1e-6)
+    st['h'] = h0.clone()
+    mine = O.beam_search(step, reorder, W, L, eos=0)
+    ps = [float(m['p']) for m in mine]
+    assert ps == sorted(ps, reverse=True)
+    for m in mine:                                      # p = sum of the per-word log-probs up to the end token
+        n = int((m['seq'] != 0).sum()) + (1 if (m['seq'] == 0).any() else 0)
+        assert abs(float(m['logps'][:min(n, L)].sum()) - float(m['p'])) < 1e-4
+    if eos_bias < -10:
+        for r, m in zip(ref, mine):
+            assert torch.equal(r['seq'], m['seq'])
