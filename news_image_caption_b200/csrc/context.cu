@@ -13,32 +13,40 @@ namespace {
 
 constexpr int kThreads = 256;
 
-template <typename TIn>
-__device__ __forceinline__ void load8_stream(const TIn* p, float (&v)[8]);
-template <>
-__device__ __forceinline__ void load8_stream<bf16>(const bf16* p, float (&v)[8]) {
+// 8 consecutive elements kept RAW in registers (4 regs for bf16, 8 for fp32) so that many layers can be in flight per
+// thread before any is consumed; streaming loads (read once: no L1 allocation)
+template <typename TIn> struct Raw8;
+template <> struct Raw8<bf16> {
   uint4 u;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
-               : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
-               : "l"(p));
-  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    v[2 * i] = __uint_as_float(w[i] << 16);
-    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  __device__ __forceinline__ void load(const bf16* p) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
+                 : "l"(p));
   }
-}
-template <>
-__device__ __forceinline__ void load8_stream<float>(const float* p, float (&v)[8]) {
+  __device__ __forceinline__ void fma_into(float w, float (&acc)[8]) const {
+    const uint32_t q[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      acc[2 * i] = fmaf(__uint_as_float(q[i] << 16), w, acc[2 * i]);
+      acc[2 * i + 1] = fmaf(__uint_as_float(q[i] & 0xffff0000u), w, acc[2 * i + 1]);
+    }
+  }
+};
+template <> struct Raw8<float> {
   float4 a, b;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
-               : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w)
-               : "l"(p));
-  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
-               : "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
-               : "l"(p + 4));
-  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-}
+  __device__ __forceinline__ void load(const float* p) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w)
+                 : "l"(p));
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p + 4));
+  }
+  __device__ __forceinline__ void fma_into(float w, float (&acc)[8]) const {
+    acc[0] = fmaf(a.x, w, acc[0]); acc[1] = fmaf(a.y, w, acc[1]); acc[2] = fmaf(a.z, w, acc[2]); acc[3] = fmaf(a.w, w, acc[3]);
+    acc[4] = fmaf(b.x, w, acc[4]); acc[5] = fmaf(b.y, w, acc[5]); acc[6] = fmaf(b.z, w, acc[6]); acc[7] = fmaf(b.w, w, acc[7]);
+  }
+};
 
 // one thread = 8 consecutive features of one (b, s) position, all layers: n_layers independent 16/32-byte loads in
 // flight per thread, fp32 accumulation in the reference's order (layer 0 first), transposed store
@@ -66,17 +74,13 @@ __global__ void __launch_bounds__(kThreads) context_mix_kernel(tnt_context_mix_p
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
     for (int l0 = 0; l0 < p.n_layers; l0 += UNROLL) {
-      float v[UNROLL][8];
+      Raw8<TIn> v[UNROLL];
 #pragma unroll
       for (int u = 0; u < UNROLL; ++u)
-        if (l0 + u < p.n_layers) load8_stream<TIn>(reinterpret_cast<const TIn*>(p.layers[l0 + u]) + off, v[u]);
+        if (l0 + u < p.n_layers) v[u].load(reinterpret_cast<const TIn*>(p.layers[l0 + u]) + off);
 #pragma unroll
       for (int u = 0; u < UNROLL; ++u)
-        if (l0 + u < p.n_layers) {
-          const float w = wsm[l0 + u];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j] = fmaf(v[u][j], w, acc[j]);
-        }
+        if (l0 + u < p.n_layers) v[u].fma_into(wsm[l0 + u], acc);
     }
     TOut* o = reinterpret_cast<TOut*>(p.out) + (static_cast<long>(s) * p.B + b) * p.E + vc * 8;
     store8(o, acc);
@@ -120,10 +124,10 @@ extern "C" int tnt_context_mix(const tnt_context_mix_params* p, tnt_stream strea
   if (total == 0) return TNT_OK;
   const int grid = static_cast<int>(std::min<long>((total + kThreads - 1) / kThreads, 8L * num_sms()));
   cudaStream_t st = as_stream(stream);
-  if (p->dtype_in == TNT_BF16 && p->dtype_out == TNT_BF16) context_mix_kernel<bf16, bf16, 5><<<grid, kThreads, 0, st>>>(*p);
-  else if (p->dtype_in == TNT_BF16) context_mix_kernel<bf16, float, 5><<<grid, kThreads, 0, st>>>(*p);
-  else if (p->dtype_out == TNT_BF16) context_mix_kernel<float, bf16, 5><<<grid, kThreads, 0, st>>>(*p);
-  else context_mix_kernel<float, float, 5><<<grid, kThreads, 0, st>>>(*p);
+  if (p->dtype_in == TNT_BF16 && p->dtype_out == TNT_BF16) context_mix_kernel<bf16, bf16, 13><<<grid, kThreads, 0, st>>>(*p);
+  else if (p->dtype_in == TNT_BF16) context_mix_kernel<bf16, float, 13><<<grid, kThreads, 0, st>>>(*p);
+  else if (p->dtype_out == TNT_BF16) context_mix_kernel<float, bf16, 7><<<grid, kThreads, 0, st>>>(*p);
+  else context_mix_kernel<float, float, 7><<<grid, kThreads, 0, st>>>(*p);
   TNT_LAUNCHED();
   return TNT_OK;
 }

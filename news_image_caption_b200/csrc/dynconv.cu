@@ -62,7 +62,25 @@ __device__ __forceinline__ void normalise_taps(int t0, int T_end, int rows, int 
 }
 
 // ------------------------------------------------------------------------------ forward
-// smem: xs [(TT+K-1)][CC] fp32, taps [TT][HG][K] fp32
+// smem: taps [kTT][HG][K] fp32, then xs [(kTT+K-1)][CC] in the INPUT dtype (bf16 halves the shared-memory traffic).
+// Each thread produces 8 channels x kNT consecutive timesteps: an input row is read from shared memory once per
+// kNT outputs instead of once per output (the kernel was shared-memory-bandwidth bound at K = 31).
+constexpr int kNT = 4;
+template <typename T>
+__device__ __forceinline__ void copy8(const T* src, T* dst) {            // 8 elements, 16-byte aligned (bf16) / 32 (fp32)
+  if (sizeof(T) == 2) {
+    *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+  } else {
+    *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+    *(reinterpret_cast<uint4*>(dst) + 1) = *(reinterpret_cast<const uint4*>(src) + 1);
+  }
+}
+template <typename T>
+__device__ __forceinline__ void zero8(T* dst) {
+  *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
+  if (sizeof(T) == 4) *(reinterpret_cast<uint4*>(dst) + 1) = make_uint4(0, 0, 0, 0);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_params p, int CC, int HG) {
   pdl_wait();
@@ -71,8 +89,8 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_param
   const int b = blockIdx.x, c0 = blockIdx.y * CC, t0 = blockIdx.z * kTT;
   const int TT = min(kTT, p.T - t0);
   const int rows = TT + K - 1;
-  float* xs = sm;
-  float* taps = sm + static_cast<size_t>(kTT + K - 1) * CC;
+  float* taps = sm;
+  T* xs = reinterpret_cast<T*>(sm + static_cast<size_t>(kTT) * HG * K);
   const T* x = reinterpret_cast<const T*>(p.x);
   const T* hist = reinterpret_cast<const T*>(p.hist);
   const T* lg = reinterpret_cast<const T*>(p.logits);
@@ -80,22 +98,14 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_param
   const int cc = min(CC, p.C - c0);
   const int nv = cc >> 3;
 
-  // stage the input window (zeros / history before t = 0)
+  // stage the input window (zeros / history before t = 0), raw
   for (int i = threadIdx.x; i < rows * nv; i += kThreads) {
     const int r = i / nv, vc = i - r * nv;
     const int ts = t0 - (K - 1) + r;
-    float v[8];
-    if (ts >= 0) {
-      load8(x + (static_cast<long>(ts) * B + b) * p.ldx + c0 + vc * 8, v);
-    } else if (hist && p.hist_len + ts >= 0) {
-      load8(hist + (static_cast<long>(p.hist_len + ts) * B + b) * p.C + c0 + vc * 8, v);
-    } else {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = 0.f;
-    }
-    float* d = xs + r * CC + vc * 8;
-    *reinterpret_cast<float4*>(d) = make_float4(v[0], v[1], v[2], v[3]);
-    *reinterpret_cast<float4*>(d + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    T* d = xs + r * CC + vc * 8;
+    if (ts >= 0) copy8(x + (static_cast<long>(ts) * B + b) * p.ldx + c0 + vc * 8, d);
+    else if (hist && p.hist_len + ts >= 0) copy8(hist + (static_cast<long>(p.hist_len + ts) * B + b) * p.C + c0 + vc * 8, d);
+    else zero8(d);
   }
   // taps: raw logits -> smem together with the input window (one memory latency), then normalised in place
   const int hg = cc / R, h0 = c0 / R;
@@ -103,21 +113,34 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_param
   __syncthreads();
   normalise_taps(t0, p.T, TT, hg, HG, K, taps);
   __syncthreads();
-  for (int i = threadIdx.x; i < TT * nv; i += kThreads) {
-    const int t = i / nv, vc = i - t * nv;
-    const float* w = taps + (t * HG + (vc * 8) / R) * K;
-    const float* xr = xs + t * CC + vc * 8;
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int j = 0; j < K; ++j) {
-      const float wj = w[j];
-      const float4 a = *reinterpret_cast<const float4*>(xr + j * CC);
-      const float4 c = *reinterpret_cast<const float4*>(xr + j * CC + 4);
-      acc[0] = fmaf(wj, a.x, acc[0]); acc[1] = fmaf(wj, a.y, acc[1]);
-      acc[2] = fmaf(wj, a.z, acc[2]); acc[3] = fmaf(wj, a.w, acc[3]);
-      acc[4] = fmaf(wj, c.x, acc[4]); acc[5] = fmaf(wj, c.y, acc[5]);
-      acc[6] = fmaf(wj, c.z, acc[6]); acc[7] = fmaf(wj, c.w, acc[7]);
+  const int ngrp = (TT + kNT - 1) / kNT;
+  for (int i = threadIdx.x; i < ngrp * nv; i += kThreads) {
+    const int tg = i / nv, vc = i - tg * nv;
+    const int tb = tg * kNT;                               // outputs tb .. tb+kNT-1 (local timesteps)
+    const float* w0 = taps + (tb * HG + (vc * 8) / R) * K;
+    const T* xr = xs + tb * CC + vc * 8;                   // output t, tap j reads local row t + j
+    float acc[kNT][8];
+#pragma unroll
+    for (int tt = 0; tt < kNT; ++tt)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[tt][e] = 0.f;
+    const int nrr = min(K + kNT - 1, rows - tb);
+    for (int rr = 0; rr < nrr; ++rr) {
+      float xv[8];
+      load8(xr + rr * CC, xv);
+#pragma unroll
+      for (int tt = 0; tt < kNT; ++tt) {
+        const int j = rr - tt;
+        if (j >= 0 && j < K && tb + tt < TT) {
+          const float wj = w0[tt * HG * K + j];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[tt][e] = fmaf(wj, xv[e], acc[tt][e]);
+        }
+      }
     }
-    store8(y + (static_cast<long>(t0 + t) * B + b) * p.ldy + c0 + vc * 8, acc);
+#pragma unroll
+    for (int tt = 0; tt < kNT; ++tt)
+      if (tb + tt < TT) store8(y + (static_cast<long>(t0 + tb + tt) * B + b) * p.ldy + c0 + vc * 8, acc[tt]);
   }
 }
 
@@ -289,7 +312,7 @@ extern "C" int tnt_dynconv_fwd(const tnt_dynconv_params* p, tnt_stream stream) {
   if (p->T == 0) return TNT_OK;
   int CC, HG;
   const int ngroups = pick_group(p->C, p->H, 256, &CC, &HG);
-  const size_t smem = (static_cast<size_t>(kTT + p->K - 1) * CC + static_cast<size_t>(kTT) * HG * p->K) * 4;
+  const size_t smem = static_cast<size_t>(kTT + p->K - 1) * CC * dtype_size(p->dtype) + static_cast<size_t>(kTT) * HG * p->K * 4;
   dim3 grid(p->B, ngroups, (p->T + kTT - 1) / kTT);
   if (p->dtype == TNT_BF16) {
     TNT_TRY(set_smem(dynconv_fwd_kernel<bf16>, smem));

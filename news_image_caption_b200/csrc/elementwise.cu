@@ -158,6 +158,97 @@ __global__ void __launch_bounds__(kWarps * 32) layernorm_bwd_kernel(tnt_layernor
   }
 }
 
+// C <= 1024: the row (x, dy) lives in registers -- one HBM read of each, no re-reads -- and every lane keeps the
+// dgamma / dbeta partials of ITS 32 channels in registers across all rows of its warp; the block combines the warps'
+// partials through shared memory once at the end (the generic kernel above issues 2*C shared atomics per row).
+template <typename T>
+__global__ void __launch_bounds__(kWarps * 32) layernorm_bwd_small_kernel(tnt_layernorm_bwd_params p) {
+  extern __shared__ float sm[];                        // [kWarps][2][C]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nv = p.C >> 3;
+  float g[4][8], dg[4][8], db[4][8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int vc = lane + 32 * i;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dg[i][j] = db[i][j] = 0.f, g[i][j] = 0.f;
+    if (vc < nv) load8(p.gamma + vc * 8, g[i]);
+  }
+  const float invC = 1.f / p.C;
+  for (int row = blockIdx.x * kWarps + warp; row < p.rows; row += gridDim.x * kWarps) {
+    const T* x = reinterpret_cast<const T*>(p.x) + static_cast<long>(row) * p.ldx;
+    const T* dy = reinterpret_cast<const T*>(p.dy) + static_cast<long>(row) * p.lddy;
+    T* dx = reinterpret_cast<T*>(p.dx) + static_cast<long>(row) * p.lddx;
+    float t[4][8], d[4][8];
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int vc = lane + 32 * i;
+      if (vc < nv) {
+        load8(x + vc * 8, t[i]);
+        load8(dy + vc * 8, d[i]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[i][j] = d[i][j] = 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sum += t[i][j];
+    }
+    const float mean = warp_sum(sum) * invC;
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (lane + 32 * i < nv) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sq = fmaf(t[i][j] - mean, t[i][j] - mean, sq);
+      }
+    const float rstd = rsqrtf(warp_sum(sq) * invC + p.eps);
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xh = (t[i][j] - mean) * rstd, dxh = d[i][j] * g[i][j];
+        t[i][j] = xh;                                  // keep x-hat
+        s1 += dxh;
+        s2 = fmaf(dxh, xh, s2);
+        dg[i][j] = fmaf(d[i][j], xh, dg[i][j]);
+        db[i][j] += d[i][j];
+      }
+    s1 = warp_sum(s1) * invC;
+    s2 = warp_sum(s2) * invC;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int vc = lane + 32 * i;
+      if (vc < nv) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (d[i][j] * g[i][j] - s1 - t[i][j] * s2);
+        store8(dx + vc * 8, o);
+      }
+    }
+  }
+  float* mine = sm + static_cast<size_t>(warp) * 2 * p.C;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int vc = lane + 32 * i;
+    if (vc < nv) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        mine[vc * 8 + j] = dg[i][j];
+        mine[p.C + vc * 8 + j] = db[i][j];
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * p.C; i += blockDim.x) {
+    float a = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) a += sm[static_cast<size_t>(w) * 2 * p.C + i];
+    atomicAdd(i < p.C ? p.dgamma + i : p.dbeta + (i - p.C), a);
+  }
+}
+
 // ------------------------------------------------------------------------------ embedding
 // adaptive.py:61-76 (pre-projected bands) + positional.py:167-211 + sum_text_field_embedder.py:117
 template <typename T>
@@ -270,7 +361,17 @@ extern "C" int tnt_layernorm_bwd(const tnt_layernorm_bwd_params* p, tnt_stream s
   if (p->rows == 0) return TNT_OK;
   const int grid = std::min((p->rows + kWarps - 1) / kWarps, 2 * num_sms());
   const size_t smem = 2 * static_cast<size_t>(p->C) * 4;
-  if (p->dtype == TNT_BF16)
+  if (p->C <= 1024) {
+    const size_t smem_s = static_cast<size_t>(kWarps) * 2 * p->C * 4;           // <= 64 KB
+    const int grid_s = std::min((p->rows + kWarps - 1) / kWarps, 4 * num_sms());
+    if (p->dtype == TNT_BF16) {
+      TNT_CUDA(cudaFuncSetAttribute(layernorm_bwd_small_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+      layernorm_bwd_small_kernel<bf16><<<grid_s, kWarps * 32, smem_s, as_stream(stream)>>>(*p);
+    } else {
+      TNT_CUDA(cudaFuncSetAttribute(layernorm_bwd_small_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+      layernorm_bwd_small_kernel<float><<<grid_s, kWarps * 32, smem_s, as_stream(stream)>>>(*p);
+    }
+  } else if (p->dtype == TNT_BF16)
     layernorm_bwd_kernel<bf16><<<grid, kWarps * 32, smem, as_stream(stream)>>>(*p);
   else
     layernorm_bwd_kernel<float><<<grid, kWarps * 32, smem, as_stream(stream)>>>(*p);
