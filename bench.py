@@ -247,7 +247,7 @@ def main():
     kv_ms, kv_n = C.c_double(0), C.c_int(0)
     L.tnt_prof_read(b'kv_proj.article', C.byref(kv_ms), C.byref(kv_n))
     xs_ms, xs_n = C.c_double(0), C.c_int(0)
-    L.tnt_prof_read(b'xattn_step.article', C.byref(xs_ms), C.byref(xs_n))
+    L.tnt_prof_read(b'xattn_step.merged', C.byref(xs_ms), C.byref(xs_n))
     L.tnt_prof_reset()
     ms = torch.tensor([e0.elapsed_time(e1)], device='cuda')
     ntok_all = torch.tensor([float(ntok)], device='cuda')
@@ -329,14 +329,14 @@ def main():
                 'share_of_step': gemm_ms / (ms_total / args.steps)}
 
     if gen:
-        # dominant kernel of a decoding step: cross-attention over the cached article K/V (1 query per head):
-        # algorithmic bytes = K and V rows of this layer for every caption, (S+2) * 2 * d * 2 B, + q/out
-        # for every LIVE key (padded article positions are never fetched; + the bias_k/v row and the zero row)
-        live = int((~ctx['article_mask']).sum()) + 2 * B_PER_GPU
-        byts = live * 2 * 1024 * 2 + B_PER_GPU * 2 * 1024 * 2
+        # dominant kernel of a decoding step: cross-attention over the cached K/V of every source of a layer (image +
+        # article in ONE launch, 1 query per head).  Algorithmic bytes = K and V rows of this layer for every LIVE key
+        # (padded article positions are never fetched; + the bias_k/v row and the zero row per source) + q / out
+        live = int((~ctx['article_mask']).sum()) + (S_IMG + 2 + 2) * B_PER_GPU
+        byts = live * 2 * 1024 * 2 + 2 * B_PER_GPU * 2 * 1024 * 2
         x_ms = xs_ms.value / max(xs_n.value, 1)
         ach = byts / (x_ms * 1e-3) / 1e9 if x_ms > 0 else 0.0
-        roofline = {'bound': 'hbm', 'kernel': 'decode-step cross-attention over the cached article K/V (one layer)',
+        roofline = {'bound': 'hbm', 'kernel': 'xattn_step_kernel: decode-step cross-attention over the cached image + article K/V of one layer (one launch)',
                     'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': None,
                     'peak_source': which + ' hbm_gbs', 'bytes_per_launch': byts, 'ms_per_launch': x_ms,
                     'launches_timed': xs_n.value, 'live_keys_per_caption': live / B_PER_GPU, 'note': 'timed on the eager step 0 of every generate call (steps 1.. replay a CUDA graph)',

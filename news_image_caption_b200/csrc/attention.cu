@@ -243,6 +243,7 @@ int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st);
 bool xattn_step_supported(const tnt_xattn_params* p);
 int xattn_fwd_step(const tnt_xattn_params* p, cudaStream_t st);
 static bool g_force_simt_attn = false;
+bool xattn_force_simt() { return g_force_simt_attn; }
 int xattn_fwd_dispatch(const tnt_xattn_params* p, cudaStream_t st) {
   if (!g_force_simt_attn && xattn_step_supported(p)) return xattn_fwd_step(p, st);      // T == 1: HBM-streaming decode kernel
   if (!g_force_simt_attn && xattn_tc_supported(p)) return xattn_fwd_tc(p, st);

@@ -36,7 +36,13 @@ __device__ __forceinline__ uint4 ldg_stream(const void* p) {
   return r;
 }
 
-__global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(tnt_xattn_params p) {
+// up to TNT_MAX_SOURCES attention problems (the sources of one decoder layer) in ONE launch: blockIdx.z picks the source
+struct StepBatch {
+  tnt_xattn_params p[TNT_MAX_SOURCES];
+};
+
+__global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(const __grid_constant__ StepBatch batch) {
+  const tnt_xattn_params& p = batch.p[blockIdx.z];
   __shared__ float sm_m[kWarps][32], sm_l[kWarps][32];
   __shared__ float sm_acc[kWarps][32][17];
   __shared__ uint8_t sm_mask[kMaxKeys];
@@ -160,6 +166,8 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(tnt_xattn_param
 
 }  // namespace
 
+int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st);
+
 bool xattn_step_supported(const tnt_xattn_params* p) {
   if (p->T != 1 || p->dtype != TNT_BF16 || p->D != 64 || (p->H % kHeadsPerCta) != 0 || p->n_extra != 0 || p->weights)
     return false;
@@ -168,9 +176,18 @@ bool xattn_step_supported(const tnt_xattn_params* p) {
   return p->S >= 1 && p->S <= kMaxKeys && (strides % 8) == 0 && aligned16(p->q) && aligned16(p->k) && aligned16(p->v) && aligned16(p->out);
 }
 
-int xattn_fwd_step(const tnt_xattn_params* p, cudaStream_t st) {
-  dim3 grid(p->B, p->H / kHeadsPerCta);
-  TNT_CUDA(launch_pdl(xattn_step_kernel, grid, dim3(kWarps * 32), 0, st, 1, *p));
+int xattn_fwd_step(const tnt_xattn_params* p, cudaStream_t st) { return xattn_fwd_step_multi(p, 1, st); }
+
+// n problems with the same B and H (the sources of one decoder layer), one launch
+int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st) {
+  TNT_CHECK_ARG(n >= 1 && n <= TNT_MAX_SOURCES, "xattn_step: %d problems", n);
+  StepBatch batch;
+  for (int i = 0; i < n; ++i) {
+    TNT_CHECK_ARG(ps[i].B == ps[0].B && ps[i].H == ps[0].H, "xattn_step: problems of one launch must share B and H");
+    batch.p[i] = ps[i];
+  }
+  dim3 grid(ps[0].B, ps[0].H / kHeadsPerCta, n);
+  TNT_CUDA(launch_pdl(xattn_step_kernel, grid, dim3(kWarps * 32), 0, st, 1, batch));
   TNT_LAUNCHED();
   return TNT_OK;
 }

@@ -9,6 +9,9 @@ namespace tnt {
 
 int xattn_check(const tnt_xattn_params* p);
 int xattn_fwd_dispatch(const tnt_xattn_params* p, cudaStream_t st);
+bool xattn_step_supported(const tnt_xattn_params* p);
+int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st);
+bool xattn_force_simt();
 
 namespace {
 inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
@@ -120,8 +123,11 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
   // multi-source cross attention: one stacked query projection, per-source attention, grouped out-proj
   TNT_TRY(linear(w.X1, d, L.wq, d, L.bq, w.Q, static_cast<long>(ns) * d, N, ns * d, d, dt, EPI_NONE, nullptr, 0, st));
   const long ldkv = static_cast<long>(c.n_layers) * 2 * d;
+  tnt_xattn_params aps[TNT_MAX_SOURCES];
+  bool all_step = T == 1;
   for (int s = 0; s < ns; ++s) {
-    tnt_xattn_params ap = {};
+    tnt_xattn_params& ap = aps[s];
+    ap = tnt_xattn_params{};
     ap.q = static_cast<const char*>(w.Q) + static_cast<size_t>(s) * d * E;
     ap.q_stride_t = static_cast<long>(B) * ns * d; ap.q_stride_b = static_cast<long>(ns) * d;
     ap.k = static_cast<const char*>(w.kv[s]) + static_cast<size_t>(l) * 2 * d * E;
@@ -142,14 +148,24 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     ap.scale = 1.0f / sqrtf(static_cast<float>(d / H));
     ap.dtype = dt;
     TNT_TRY(xattn_check(&ap));
-    int pid = -1;
-    if (prof_enabled()) {
-      char pname[48];
-      snprintf(pname, sizeof(pname), T == 1 ? "xattn_step.%s" : "xattn.%s", c.source_names[s]);
-      pid = prof_begin(pname, st);
-    }
-    TNT_TRY(xattn_fwd_dispatch(&ap, st));
+    all_step = all_step && !xattn_force_simt() && xattn_step_supported(&ap);
+  }
+  if (all_step) {
+    const int pid = prof_enabled() ? prof_begin("xattn_step.merged", st) : -1;   // -1 while a graph is being captured
+    TNT_TRY(xattn_fwd_step_multi(aps, ns, st));          // decode step: every source of the layer in one launch
     prof_end(pid, st);
+  } else {
+    for (int s = 0; s < ns; ++s) {
+      const tnt_xattn_params& ap = aps[s];
+      int pid = -1;
+      if (prof_enabled()) {
+        char pname[48];
+        snprintf(pname, sizeof(pname), T == 1 ? "xattn_step.%s" : "xattn.%s", c.source_names[s]);
+        pid = prof_begin(pname, st);
+      }
+      TNT_TRY(xattn_fwd_dispatch(&ap, st));
+      prof_end(pid, st);
+    }
   }
   TNT_TRY(linear(w.AO, static_cast<long>(ns) * d, L.wo, d, L.bo, w.CAT, static_cast<long>(ns) * d, N, d, d, dt, EPI_RESIDUAL,
                  w.X1, d, st, ns, d, static_cast<long>(d) * d, d, 0, d));
