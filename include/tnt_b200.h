@@ -78,6 +78,9 @@ typedef struct {
   int dtype_in, dtype_out, epilogue;
   int layout;                         /* tnt_gemm_layout; with TNT_TN `m_dyn` bounds the reduction length K */
   float alpha;                        /* scales the accumulator before bias / epilogue; 0 means 1 */
+  /* optional L2 prefetch hint: `prefetch_bytes` bytes at `prefetch` (16-byte aligned, e.g. the weights of the NEXT
+   * GEMM of a latency-bound chain) are requested into L2 (cp.async.bulk.prefetch.L2) by the kernel's prologue */
+  const void* prefetch; uint64_t prefetch_bytes;
 } tnt_linear_params;
 int tnt_linear_fwd(const tnt_linear_params* p, tnt_stream stream);
 

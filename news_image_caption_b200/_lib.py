@@ -23,7 +23,8 @@ class LinearParams(C.Structure):
     _fields_ = [('a', vp), ('lda', i64), ('w', vp), ('ldw', i64), ('bias', vp), ('residual', vp), ('ldr', i64),
                 ('c', vp), ('ldc', i64), ('M', i32), ('N', i32), ('K', i32), ('m_dyn', vp), ('groups', i32),
                 ('stride_a', i64), ('stride_w', i64), ('stride_bias', i64), ('stride_res', i64), ('stride_c', i64),
-                ('dtype_in', i32), ('dtype_out', i32), ('epilogue', i32), ('layout', i32), ('alpha', f32)]
+                ('dtype_in', i32), ('dtype_out', i32), ('epilogue', i32), ('layout', i32), ('alpha', f32),
+                ('prefetch', vp), ('prefetch_bytes', C.c_uint64)]
 
 
 class DynconvParams(C.Structure):
@@ -159,6 +160,7 @@ _SIGS = {
     'tnt_debug_gemm_cta_group': (None, [i32]),
     'tnt_debug_pdl': (None, [i32]),
     'tnt_debug_gemm_tile_n': (None, [i32]),
+    'tnt_debug_gemm_stages': (None, [i32]),
     'tnt_debug_force_simt_attention': (None, [i32]),
     'tnt_debug_force_simt_attention_bwd': (None, [i32]),
 }

@@ -18,12 +18,13 @@ inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
 
 int linear(const void* a, long lda, const void* w, long ldw, const float* bias, void* c, long ldc, int M, int N, int K,
            int dtype, int epi, const void* res, long ldr, cudaStream_t st, int groups = 1, long sa = 0, long sw = 0,
-           long sb = 0, long sr = 0, long sc = 0) {
+           long sb = 0, long sr = 0, long sc = 0, const void* pf = nullptr, size_t pf_bytes = 0) {
   tnt_linear_params p = {};
   p.a = a; p.lda = lda; p.w = w; p.ldw = ldw; p.bias = bias; p.residual = res; p.ldr = ldr; p.c = c; p.ldc = ldc;
   p.M = M; p.N = N; p.K = K; p.groups = groups;
   p.stride_a = sa; p.stride_w = sw; p.stride_bias = sb; p.stride_res = sr; p.stride_c = sc;
   p.dtype_in = dtype; p.dtype_out = dtype; p.epilogue = epi;
+  p.prefetch = pf; p.prefetch_bytes = pf_bytes;
   return launch_gemm(&p, -1, nullptr, nullptr, st);
 }
 
@@ -104,8 +105,14 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
   const int ldl = D->ld_logits(L.K);
   const size_t E = D->esz();
   // conv block: linear1 + GLU -> tap logits -> dynamic conv -> linear2 + residual -> LayerNorm
-  TNT_TRY(linear(Xin, d, L.w1, d, L.b1, w.h, d, N, 2 * d, d, dt, EPI_GLU, nullptr, 0, st));
-  TNT_TRY(linear(w.h, d, L.wtap, d, nullptr, w.logits, ldl, N, H * L.K, d, dt, EPI_NONE, nullptr, 0, st));
+  // each GEMM of the chain asks for the NEXT GEMM's weights to be staged in L2 while it runs (the step's K/V traffic
+  // leaves no weight L2-resident from one step to the next; the small-M GEMMs are otherwise DRAM-latency bound)
+  const size_t dd = static_cast<size_t>(d) * d * E;
+  const void* next_w1 = l + 1 < c.n_layers ? D->layers[l + 1].w1 : D->ada.head_w;
+  const size_t next_w1_bytes = l + 1 < c.n_layers ? 2 * dd : static_cast<size_t>(D->ada.cuts.cut[0] + D->ada.cuts.n - 1) * d * E;
+  TNT_TRY(linear(Xin, d, L.w1, d, L.b1, w.h, d, N, 2 * d, d, dt, EPI_GLU, nullptr, 0, st, 1, 0, 0, 0, 0, 0, L.wtap,
+                 static_cast<size_t>(H) * L.K * d * E));
+  TNT_TRY(linear(w.h, d, L.wtap, d, nullptr, w.logits, ldl, N, H * L.K, d, dt, EPI_NONE, nullptr, 0, st, 1, 0, 0, 0, 0, 0, L.w2, dd));
   if (ring || pos) {
     TNT_CHECK_ARG(T == 1, "decoder: incremental layer call needs T == 1");
     tnt_dynconv_step_params sp = {};
@@ -118,10 +125,11 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     cp.T = T; cp.B = B; cp.C = d; cp.H = H; cp.K = L.K; cp.dtype = dt;
     TNT_TRY(tnt_dynconv_fwd(&cp, st));
   }
-  TNT_TRY(linear(w.cbuf, d, L.w2, d, L.b2, w.ybuf, d, N, d, d, dt, EPI_RESIDUAL, Xin, d, st));
+  TNT_TRY(linear(w.cbuf, d, L.w2, d, L.b2, w.ybuf, d, N, d, d, dt, EPI_RESIDUAL, Xin, d, st, 1, 0, 0, 0, 0, 0, L.wq, ns * dd));
   TNT_TRY(layernorm(w.ybuf, w.X1, d, L.ln_conv_g, L.ln_conv_b, N, d, 1, dt, 0, 0, st));
   // multi-source cross attention: one stacked query projection, per-source attention, grouped out-proj
-  TNT_TRY(linear(w.X1, d, L.wq, d, L.bq, w.Q, static_cast<long>(ns) * d, N, ns * d, d, dt, EPI_NONE, nullptr, 0, st));
+  TNT_TRY(linear(w.X1, d, L.wq, d, L.bq, w.Q, static_cast<long>(ns) * d, N, ns * d, d, dt, EPI_NONE, nullptr, 0, st, 1, 0, 0, 0, 0, 0,
+                 L.wo, ns * dd));
   const long ldkv = static_cast<long>(c.n_layers) * 2 * d;
   tnt_xattn_params aps[TNT_MAX_SOURCES];
   bool all_step = T == 1;
@@ -168,13 +176,15 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     }
   }
   TNT_TRY(linear(w.AO, static_cast<long>(ns) * d, L.wo, d, L.bo, w.CAT, static_cast<long>(ns) * d, N, d, d, dt, EPI_RESIDUAL,
-                 w.X1, d, st, ns, d, static_cast<long>(d) * d, d, 0, d));
+                 w.X1, d, st, ns, d, static_cast<long>(d) * d, d, 0, d, L.wc, ns * dd));
   TNT_TRY(layernorm(w.CAT, w.CATln, d, L.ln_src_g, L.ln_src_b, N * ns, d, ns, dt, 0, 0, st));
   TNT_TRY(linear(w.CATln, static_cast<long>(ns) * d, L.wc, static_cast<long>(ns) * d, L.bc, w.X0, d, N, d, ns * d, dt, EPI_NONE,
-                 nullptr, 0, st));
+                 nullptr, 0, st, 1, 0, 0, 0, 0, 0, L.wf1, static_cast<size_t>(c.ffn) * d * E));
   // feed-forward
-  TNT_TRY(linear(w.X0, d, L.wf1, d, L.bf1, w.F, c.ffn, N, c.ffn, d, dt, EPI_RELU, nullptr, 0, st));
-  TNT_TRY(linear(w.F, c.ffn, L.wf2, c.ffn, L.bf2, w.ybuf2, d, N, d, c.ffn, dt, EPI_RESIDUAL, w.X0, d, st));
+  TNT_TRY(linear(w.X0, d, L.wf1, d, L.bf1, w.F, c.ffn, N, c.ffn, d, dt, EPI_RELU, nullptr, 0, st, 1, 0, 0, 0, 0, 0, L.wf2,
+                 static_cast<size_t>(c.ffn) * d * E));
+  TNT_TRY(linear(w.F, c.ffn, L.wf2, c.ffn, L.bf2, w.ybuf2, d, N, d, c.ffn, dt, EPI_RESIDUAL, w.X0, d, st, 1, 0, 0, 0, 0, 0, next_w1,
+                 next_w1_bytes));
   TNT_TRY(layernorm(w.ybuf2, Xout, d, L.ln_f_g, L.ln_f_b, N, d, 1, dt, transpose_out ? T : 0, transpose_out ? B : 0, st));
   return TNT_OK;
 }

@@ -4,6 +4,7 @@
 //   fp32: plain SIMT fp32 kernel (parity mode; also the in-library cross-check for the tcgen05 path).
 // Replaces GehringLinear / TiedLinear / F.linear: ttl/tell/modules/linear.py:7-50.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
@@ -65,6 +66,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmW);
+  }
+  if (warp == 3 && lane == 0 && g.pf_bytes) {
+    // constant data (the next GEMM's weights): safe before the PDL wait; every CTA requests its slice into L2
+    const unsigned long long chunk = ((g.pf_bytes + gridDim.x - 1) / gridDim.x + 15) & ~15ull;
+    const unsigned long long off = blockIdx.x * chunk;
+    if (off < g.pf_bytes) ptx::prefetch_l2_bulk(g.pf + off, static_cast<uint32_t>(min(chunk, g.pf_bytes - off) & ~15ull));
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
@@ -425,6 +432,7 @@ int make_tmap_bf16_3d(CUtensorMap* tm, const void* base, long d0, long d1, long 
 }
 
 static int g_cta_group = 0;   // test hook: 0 = automatic, 1 / 2 = force the single-CTA / CTA-pair kernel
+static int g_force_stages = 0;   // tuning hook: cap the smem ring depth
 static int g_force_bn = 0;    // tuning hook: force the tile width (32..256; CTA pair: 64..256)
 
 // tile shape the tcgen05 dispatcher uses: CTA-pair 256 x 256 tiles when the problem fills the 74 SM pairs for
@@ -479,7 +487,8 @@ static int launch_tc_cg(const GemmArgs& g, int BN, cudaStream_t st) {
   if (g.b_mn) TNT_TRY(make_tmap_bf16(&tmW, g.w, g.N, g.K, g.ldw, g.groups, g.sw, 64));
   else TNT_TRY(make_tmap_bf16(&tmW, g.w, g.K, g.N, g.ldw, g.groups, g.sw, BNL));
   const int stage_bytes = tc::A_STAGE_BYTES + BNL * tc::BK * 2;
-  const int stages = std::min(tc::kMaxStages, (tc::kSmemBudget - 4096) / stage_bytes);
+  int stages = std::min(tc::kMaxStages, (tc::kSmemBudget - 4096) / stage_bytes);
+  if (g_force_stages > 0) stages = std::min(stages, g_force_stages);
   const int smem = stages * stage_bytes + 1024 + 512 + 2048;     // ring + alignment slack + barriers + bias staging
   const int n_tiles = (g.N + BN - 1) / BN;
   const long tiles = static_cast<long>(g.groups) * ((g.M + tc::BM * CG - 1) / (tc::BM * CG)) * n_tiles;
@@ -555,6 +564,9 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
   g.alpha = p->alpha != 0.f ? p->alpha : 1.f;
   g.row_lse = lse ? lse->row_lse : nullptr;
   g.gscale = lse ? lse->gscale : 1.f;
+  static const bool pf_on = [] { const char* e = getenv("TNT_L2_PREFETCH"); return !(e && e[0] == '0'); }();
+  g.pf = (pf_on && p->prefetch && aligned16(p->prefetch)) ? static_cast<const char*>(p->prefetch) : nullptr;
+  g.pf_bytes = g.pf ? (p->prefetch_bytes & ~15ull) : 0;
   TNT_CHECK_ARG(epi != EPI_SMGRAD || (lse && lse->row_lse && lse->target), "smgrad: missing row statistics");
   TNT_CHECK_ARG(epi != EPI_LSE || (lse && lse->partials && (lse->n_lse >= p->N || lse->side)), "lse: missing buffers");
   const size_t eo = dtype_size(p->dtype_out);
@@ -594,4 +606,5 @@ extern "C" int tnt_linear_fwd(const tnt_linear_params* p, tnt_stream stream) {
 }
 extern "C" void tnt_debug_force_simt_gemm(int on) { tnt::gemm_force_simt(on != 0); }
 extern "C" void tnt_debug_gemm_cta_group(int cg) { tnt::g_cta_group = (cg == 1 || cg == 2) ? cg : 0; }
+extern "C" void tnt_debug_gemm_stages(int n) { tnt::g_force_stages = n > 0 ? n : 0; }
 extern "C" void tnt_debug_gemm_tile_n(int bn) { tnt::g_force_bn = (bn == 32 || bn == 64 || bn == 128 || bn == 256) ? bn : 0; }

@@ -26,6 +26,8 @@ struct GemmArgs {
   // EPI_SMGRAD: out[m, n] = gscale * (exp(z - row_lse[m]) - (n == target[m])); rows in [M_dyn, M) get zeros
   const float* row_lse;
   float gscale;
+  // L2 prefetch hint (weights of the next GEMM of a chain), issued by the prologue
+  const char* pf; unsigned long long pf_bytes;
 };
 
 struct LseExtra {

@@ -109,6 +109,11 @@ __device__ __forceinline__ void tma_load_3d_pair(void* smem, const void* tmap, u
       : "memory");
 }
 
+// asynchronous L2 prefetch of a contiguous global range (addr 16-byte aligned, bytes a multiple of 16)
+__device__ __forceinline__ void prefetch_l2_bulk(const void* gptr, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gptr), "r"(bytes) : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05 / TMEM
 template <uint32_t kCols>
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst) {   // one full warp
