@@ -151,6 +151,37 @@ def test_linear_cta_pair(ops, M, N, K):
         L.tnt_debug_gemm_cta_group(0)
 
 
+@pytest.mark.parametrize('M,N,K,S', [(256, 1024, 4096, -1), (256, 1024, 2048, -1), (1, 64, 2048, -1), (200, 1000, 4096 + 64, 4),
+                                     (130, 96, 1024, 2), (64, 320, 8192, 8), (300, 40, 3000 + 8, 3)])
+def test_linear_split_k(ops, M, N, K, S):
+    """The cluster split-K kernel (decode-step GEMMs: few rows, long K) against fp64 and the persistent kernel:
+    automatic plan (S = -1) and forced split factors, ragged M / N / K, every epilogue it serves."""
+    from news_image_caption_b200 import _lib
+    g = torch.Generator().manual_seed(M + 7 * N + K)
+    a = torch.randn(M, K, generator=g).bfloat16()
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).bfloat16()
+    b = torch.randn(N, generator=g)
+    r = torch.randn(M, N, generator=g).bfloat16()
+    z = a.double() @ w.double().t() + b.double()
+    L = _lib.lib()
+    L.tnt_debug_gemm_split_k(0)
+    try:
+        one = ops.linear(a.cuda(), w.cuda(), b.cuda(), out_dtype=torch.float32)
+        L.tnt_debug_gemm_split_k(S)
+        two = ops.linear(a.cuda(), w.cuda(), b.cuda(), out_dtype=torch.float32)
+        assert rel_err(two, z) < 8e-3
+        assert rel_err(two, one) < 2e-5          # same products, different fp32 summation order
+        assert rel_err(ops.linear(a.cuda(), w.cuda(), None), z - b.double()) < 1e-2
+        assert rel_err(ops.linear(a.cuda(), w.cuda(), b.cuda(), _lib.EPI_RELU), z.relu()) < 1e-2
+        assert rel_err(ops.linear(a.cuda(), w.cuda(), b.cuda(), _lib.EPI_RESIDUAL, residual=r.cuda()), z + r.double()) < 1e-2
+        if N % 2 == 0:
+            wi = ops.wn_fold(w.float().cuda(), None, glu_interleave=True, dtype=torch.bfloat16)
+            bi = ops.glu_interleave_bias(b.cuda())
+            assert rel_err(ops.linear(a.cuda(), wi, bi, _lib.EPI_GLU), F.glu(z, dim=-1)) < 1e-2
+    finally:
+        L.tnt_debug_gemm_split_k(-1)
+
+
 def test_wn_fold(ops):
     g = torch.Generator().manual_seed(2)
     v, gg = torch.randn(64, 40, generator=g), torch.randn(64, 1, generator=g)

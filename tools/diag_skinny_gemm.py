@@ -31,3 +31,12 @@ for K in (512, 1024, 2048, 4096, 8192):
             row.append('BN%d/st%d %5.1f' % (bn, st, t(a, w, b)))
     L.tnt_debug_gemm_tile_n(0); L.tnt_debug_gemm_cta_group(0); L.tnt_debug_gemm_stages(0)
     print('M=256 N=1024 K=%5d us: %s' % (K, ' | '.join(row)), flush=True)
+# cluster split-K (gemm_splitk.cu) against the persistent kernel at its automatic tile
+for (M, N, K) in ((256, 1024, 2048), (256, 1024, 4096), (256, 4096, 1024), (256, 1024, 8192), (64, 1024, 4096), (512, 1024, 4096)):
+    a = torch.randn(M, K, device='cuda').bfloat16(); w = (torch.randn(N, K, device='cuda') / K ** 0.5).bfloat16(); b = torch.randn(N, device='cuda')
+    row = []
+    for S in (0, -1, 2, 3, 4, 6, 8):
+        L.tnt_debug_gemm_split_k(S)
+        row.append('S=%d %5.1f' % (S, t(a, w, b)))
+    L.tnt_debug_gemm_split_k(-1)
+    print('split-K M=%d N=%d K=%d us: %s' % (M, N, K, ' | '.join(row)), flush=True)
