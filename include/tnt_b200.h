@@ -58,6 +58,38 @@ typedef enum {
   TNT_EPI_RELU_BWD = 5   /* acc * (residual[M,N] > 0): gradient through relu, residual = the saved relu output */
 } tnt_epilogue;
 
+/* ------------------------------------------------------------------------------------------
+ * Dropout (training mode; F.dropout sites of decoder_flattened.py:109,283,289,308,326,340,342, dynamic.py:305,
+ * multi_head.py:463).  Counter based: element `index` of dropout site `site` is KEPT iff
+ *     tnt_dropout_bits(seed, site, index) >= (uint32) (p * 2^32)
+ * and kept values are scaled by 1 / (1 - p).  Nothing is stored: the backward kernels recompute the mask from
+ * (seed, site, index).  p == 0 (a zeroed struct) switches the site off.  tnt_dropout_bits is a host function so
+ * that a test / oracle can reproduce every mask bit for bit.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  float p;                /* drop probability in [0, 1) */
+  uint32_t site;          /* which dropout call of the model (TNT_DROP_SITE) */
+  uint64_t seed;
+  int64_t ld;             /* GEMM epilogues: index = group * group_stride + row * ld + column; 0 means ld = N */
+  int64_t group_stride;
+} tnt_dropout;
+uint32_t tnt_dropout_bits(uint64_t seed, uint32_t site, uint64_t index);
+/* out[r, c] = dropout(in[r, c]) (+ residual[r, c]); index = r * d.ld + c (d.ld == 0: cols).  In-place allowed. */
+int tnt_dropout_apply(const void* in, int64_t ldi, const void* residual, int64_t ldr, void* out, int64_t ldo, int rows,
+                      int cols, int dtype, const tnt_dropout* d, tnt_stream stream);
+/* dropout sites of the decoder engine: TNT_DROP_SITE(layer, kind) */
+enum {
+  TNT_DROP_INPUT = 0,      /* layer input before linear1 (input_dropout), index (t*B+b)*d + c */
+  TNT_DROP_TAPS = 1,       /* DynamicConv taps after their soft-max (weight_dropout), index ((t*B+b)*H + h)*K + j */
+  TNT_DROP_CONV_OUT = 2,   /* linear2 output before the residual (dropout), index (t*B+b)*d + c */
+  TNT_DROP_ATTN_OUT = 3,   /* out_proj output of source s before the residual, index (t*B+b)*(n_src*d) + s*d + c */
+  TNT_DROP_FFN_OUT = 4,    /* fc2 output before the residual, index (t*B+b)*d + c */
+  TNT_DROP_RELU = 5,       /* fc1 output after ReLU (relu_dropout), index (t*B+b)*ffn + c */
+  TNT_DROP_ATTN_PROB = 6   /* + source: attention probabilities, index ((b*H + h)*T + t)*(S+2) + key */
+};
+#define TNT_DROP_SITE(layer, kind) ((uint32_t)((layer) * 16 + (kind)))
+#define TNT_DROP_SITE_EMBED 0xFFFFu   /* embedder output, index (t*B+b)*d + c */
+
 /* operand layouts (backward passes reuse the forward weights without transposed copies):
  *   TNT_NT  C[M,N] = A[M,K] . W[N,K]^T     forward        (W = nn.Linear weight [out, in])
  *   TNT_NN  C[M,N] = A[M,K] . W[K,N]       data gradient  dX = dY . W
@@ -81,6 +113,7 @@ typedef struct {
   /* optional L2 prefetch hint: `prefetch_bytes` bytes at `prefetch` (16-byte aligned, e.g. the weights of the NEXT
    * GEMM of a latency-bound chain) are requested into L2 (cp.async.bulk.prefetch.L2) by the kernel's prologue */
   const void* prefetch; uint64_t prefetch_bytes;
+  tnt_dropout drop;                   /* TNT_EPI_RESIDUAL: dropout(a.w^T + bias) + residual; TNT_EPI_RELU: dropout(relu(.)) */
 } tnt_linear_params;
 int tnt_linear_fwd(const tnt_linear_params* p, tnt_stream stream);
 
@@ -109,6 +142,7 @@ typedef struct {
   const void* hist; int hist_len;
   int T, B, C, H, K;
   int dtype;
+  tnt_dropout drop;                   /* weight_dropout on the soft-maxed taps (dynamic.py:305) */
 } tnt_dynconv_params;
 int tnt_dynconv_fwd(const tnt_dynconv_params* p, tnt_stream stream);
 
@@ -120,6 +154,7 @@ typedef struct {
   void* dlogits;  int64_t lddl;       /* [T*B, H*K] gradient w.r.t. the tap logits */
   int T, B, C, H, K;
   int dtype;
+  tnt_dropout drop;                   /* the forward call's tap dropout */
 } tnt_dynconv_bwd_params;
 int tnt_dynconv_bwd(const tnt_dynconv_bwd_params* p, tnt_stream stream);
 
@@ -242,6 +277,8 @@ typedef struct {
   float* lse;         /* optional [B, H, T] fp32: log-sum-exp of the scaled, masked scores (saved for the backward) */
   int kv_group;       /* beam search: query rows b*kv_group .. +kv_group-1 share the k / v / mask of batch entry b
                          (B counts query rows; 0 or 1 = one k / v entry per query row) */
+  tnt_dropout drop;   /* dropout on the probabilities (multi_head.py:463), index ((b*H + h)*T + t)*(S + n_extra) + key;
+                         the soft-max normaliser (and `lse`) are those of the un-dropped probabilities */
 } tnt_xattn_params;
 int tnt_xattn_fwd(const tnt_xattn_params* p, tnt_stream stream);
 
@@ -363,7 +400,7 @@ int tnt_decoder_generate(tnt_decoder* d, const int64_t* seed, const tnt_contexts
 
 /* One training step (kernel group 4 + the forward): teacher-forced forward keeping activations,
  * AdaptiveLoss, and the backward pass through loss, layers, K/V projections and embedding bands.
- *   forward / loss : as tnt_decoder_forward + tnt_decoder_nll (dropout p = 0)
+ *   forward / loss : as tnt_decoder_forward + tnt_decoder_nll, with the dropout of tnt_decoder_set_dropout
  *   gradients      : d(loss_scale * sum-NLL)/d(parameter), fp32, WRITTEN into the buffer registered for each
  *                    reference state_dict key with tnt_decoder_set_grad (same shapes as the parameters;
  *                    weight_norm'ed linears receive weight_g / weight_v gradients, linear.py:30-33).  The tied
@@ -372,6 +409,14 @@ int tnt_decoder_generate(tnt_decoder* d, const int64_t* seed, const tnt_contexts
  *   out2           : [loss sum (nats, unscaled), number of non-pad targets]
  * The parameter pointers given to tnt_decoder_load must still be valid (the backward reads weight_v/_g and
  * the band tables).  Data-parallel training all-reduces the gradient buffers afterwards. */
+/* Dropout of the training step (config.yaml:51-69: dropout, input_dropout, weight_dropout, attention_dropout,
+ * relu_dropout).  All zero (the default) = the parity configuration.  Step k after this call (k = 0, 1, ...) draws
+ * its masks with seed + k.  adaptive_softmax_dropout is 0 in every reference config and is not supported. */
+typedef struct {
+  float dropout, input_dropout, weight_dropout, attention_dropout, relu_dropout;
+  uint64_t seed;
+} tnt_dropout_config;
+int tnt_decoder_set_dropout(tnt_decoder* d, const tnt_dropout_config* cfg);
 size_t tnt_decoder_train_workspace_bytes(const tnt_decoder* d, int B, int T, const int* S);
 int tnt_decoder_set_grad(tnt_decoder* d, const char* key, float* grad);
 int tnt_decoder_train_step(tnt_decoder* d, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,

@@ -19,23 +19,43 @@ class TntError(RuntimeError):
     pass
 
 
+class Dropout(C.Structure):
+    """tnt_dropout: counter-based dropout site (p == 0: off)."""
+    _fields_ = [('p', f32), ('site', C.c_uint32), ('seed', C.c_uint64), ('ld', i64), ('group_stride', i64)]
+
+
+class DropoutConfig(C.Structure):
+    """tnt_dropout_config: the decoder's training dropout (config.yaml:51-69)."""
+    _fields_ = [('dropout', f32), ('input_dropout', f32), ('weight_dropout', f32), ('attention_dropout', f32),
+                ('relu_dropout', f32), ('seed', C.c_uint64)]
+
+
+DROP_INPUT, DROP_TAPS, DROP_CONV_OUT, DROP_ATTN_OUT, DROP_FFN_OUT, DROP_RELU, DROP_ATTN_PROB = range(7)
+DROP_SITE_EMBED = 0xFFFF
+
+
+def drop_site(layer, kind):
+    return layer * 16 + kind
+
+
 class LinearParams(C.Structure):
     _fields_ = [('a', vp), ('lda', i64), ('w', vp), ('ldw', i64), ('bias', vp), ('residual', vp), ('ldr', i64),
                 ('c', vp), ('ldc', i64), ('M', i32), ('N', i32), ('K', i32), ('m_dyn', vp), ('groups', i32),
                 ('stride_a', i64), ('stride_w', i64), ('stride_bias', i64), ('stride_res', i64), ('stride_c', i64),
                 ('dtype_in', i32), ('dtype_out', i32), ('epilogue', i32), ('layout', i32), ('alpha', f32),
-                ('prefetch', vp), ('prefetch_bytes', C.c_uint64)]
+                ('prefetch', vp), ('prefetch_bytes', C.c_uint64), ('drop', Dropout)]
 
 
 class DynconvParams(C.Structure):
     _fields_ = [('x', vp), ('ldx', i64), ('logits', vp), ('ldl', i64), ('y', vp), ('ldy', i64), ('hist', vp),
-                ('hist_len', i32), ('T', i32), ('B', i32), ('C', i32), ('H', i32), ('K', i32), ('dtype', i32)]
+                ('hist_len', i32), ('T', i32), ('B', i32), ('C', i32), ('H', i32), ('K', i32), ('dtype', i32),
+                ('drop', Dropout)]
 
 
 class DynconvBwdParams(C.Structure):
     _fields_ = [('x', vp), ('ldx', i64), ('logits', vp), ('ldl', i64), ('dy', vp), ('lddy', i64), ('dx', vp),
                 ('lddx', i64), ('dlogits', vp), ('lddl', i64), ('T', i32), ('B', i32), ('C', i32), ('H', i32),
-                ('K', i32), ('dtype', i32)]
+                ('K', i32), ('dtype', i32), ('drop', Dropout)]
 
 
 class DynconvStepParams(C.Structure):
@@ -74,7 +94,8 @@ class XattnParams(C.Structure):
                 ('k_stride_b', i64), ('v', vp), ('v_stride_s', i64), ('v_stride_b', i64), ('out', vp),
                 ('o_stride_t', i64), ('o_stride_b', i64), ('mask', vp), ('m_stride_b', i64), ('m_stride_t', i64),
                 ('bias_k', vp), ('bias_v', vp), ('weights', vp), ('B', i32), ('T', i32), ('S', i32), ('H', i32),
-                ('D', i32), ('n_extra', i32), ('mask_mode', i32), ('scale', f32), ('dtype', i32), ('mask_S', i32), ('lse', vp), ('kv_group', i32)]
+                ('D', i32), ('n_extra', i32), ('mask_mode', i32), ('scale', f32), ('dtype', i32), ('mask_S', i32), ('lse', vp), ('kv_group', i32),
+                ('drop', Dropout)]
 
 
 class XattnBwdParams(C.Structure):
@@ -150,6 +171,9 @@ _SIGS = {
     'tnt_decoder_score_host': (i32, [vp, vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp, C.c_size_t, vp]),
     'tnt_decoder_score_host_submit': (i32, [vp, i32, vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp, C.c_size_t, vp]),
     'tnt_decoder_score_host_wait': (i32, [vp, i32]),
+    'tnt_dropout_bits': (C.c_uint32, [C.c_uint64, C.c_uint32, C.c_uint64]),
+    'tnt_dropout_apply': (i32, [vp, i64, vp, i64, vp, i64, i32, i32, i32, C.POINTER(Dropout), vp]),
+    'tnt_decoder_set_dropout': (i32, [vp, C.POINTER(DropoutConfig)]),
     'tnt_decoder_train_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
     'tnt_decoder_set_grad': (i32, [vp, C.c_char_p, vp]),
     'tnt_decoder_train_step': (i32, [vp, vp, vp, C.POINTER(Contexts), f32, vp, vp, C.c_size_t, vp]),

@@ -86,7 +86,7 @@ __device__ __forceinline__ void tile_scores(const tnt_xattn_params& p, const flo
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kThreads) xattn_fwd_kernel(tnt_xattn_params p) {
+__global__ void __launch_bounds__(kThreads) xattn_fwd_kernel(tnt_xattn_params p, DropSpec dr) {
   extern __shared__ float sm[];
   const int D = p.D, ndd = (D + 31) / 32;
   float* qs = sm;
@@ -146,8 +146,15 @@ __global__ void __launch_bounds__(kThreads) xattn_fwd_kernel(tnt_xattn_params p)
       m[qi] = mn;
 #pragma unroll
       for (int dd = 0; dd < kMaxDD; ++dd) acc[qi][dd] *= corr;
-      pw[qi * kTK + lane] = p0;
-      pw[qi * kTK + lane + 32] = p1;
+      if (dr.thr) {      // dropout on the probabilities: the normaliser l stays that of the un-dropped soft-max
+        const unsigned long long i0 =
+            ((static_cast<unsigned long long>(b) * p.H + h) * p.T + t0 + qw + qi) * S2 + key0 + lane;
+        pw[qi * kTK + lane] = drop_val(dr, i0, p0);
+        pw[qi * kTK + lane + 32] = drop_val(dr, i0 + 32, p1);
+      } else {
+        pw[qi * kTK + lane] = p0;
+        pw[qi * kTK + lane + 32] = p1;
+      }
     }
     __syncwarp();
     for (int kk = 0; kk < kTK; ++kk) {
@@ -214,11 +221,11 @@ int xattn_fwd_simt(const tnt_xattn_params* p, cudaStream_t st) {
   if (p->dtype == TNT_BF16) {
     if (smem > 48 * 1024)
       TNT_CUDA(cudaFuncSetAttribute(xattn_fwd_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    xattn_fwd_kernel<bf16><<<grid, kThreads, smem, st>>>(*p);
+    xattn_fwd_kernel<bf16><<<grid, kThreads, smem, st>>>(*p, make_drop(p->drop));
   } else {
     if (smem > 48 * 1024)
       TNT_CUDA(cudaFuncSetAttribute(xattn_fwd_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    xattn_fwd_kernel<float><<<grid, kThreads, smem, st>>>(*p);
+    xattn_fwd_kernel<float><<<grid, kThreads, smem, st>>>(*p, make_drop(p->drop));
   }
   TNT_LAUNCHED();
   return TNT_OK;
@@ -228,6 +235,8 @@ int xattn_check(const tnt_xattn_params* p) {
   TNT_CHECK_ARG(p && p->q && p->k && p->v && p->out, "xattn: null pointer");
   TNT_CHECK_ARG(p->B > 0 && p->T >= 0 && p->S >= 0 && p->H > 0, "xattn: bad shape");
   TNT_CHECK_ARG(p->D % 8 == 0 && p->D <= 128, "xattn: head dim %d must be a multiple of 8, <= 128", p->D);
+  TNT_CHECK_ARG(p->drop.p >= 0.f && p->drop.p < 1.f, "xattn: dropout p = %f", p->drop.p);
+  TNT_CHECK_ARG(!(p->drop.p > 0.f) || !p->weights, "xattn: the head-averaged weights output is not available with dropout");
   TNT_CHECK_ARG(p->n_extra == 0 || p->n_extra == 2, "xattn: n_extra must be 0 or 2");
   TNT_CHECK_ARG(p->n_extra == 0 || (p->bias_k && p->bias_v), "xattn: bias_k / bias_v missing");
   TNT_CHECK_ARG(p->mask_mode == TNT_MASK_NONE || p->mask, "xattn: mask missing");

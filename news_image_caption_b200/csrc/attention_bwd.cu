@@ -18,6 +18,7 @@ struct BwdArgs {
   tnt_xattn_params f;
   const void* dout; void* dq; void* dk; void* dv;
   float* scratch;               // [B, H, T, D] fp32
+  DropSpec drop;                // the forward's dropout on the probabilities
 };
 
 template <typename T>
@@ -160,8 +161,12 @@ __global__ void __launch_bounds__(kThreads) xattn_bwd_kernel(BwdArgs a) {
           const int kk = kg * 4 + e;
           const float z = qok ? apply_mask(p, b, t0 + qi, key0 + kk, s[e]) : -INFINITY;
           const float pr = (qok && z != -INFINITY && L != INFINITY) ? __expf(z - L) : 0.f;
-          Ps[qi * 33 + kk] = pr;
-          dSs[qi * 33 + kk] = pr * (dp[e] - dl);
+          // dropout mask m (0 or 1/(1-p)) of the forward: out = (P . m) V, so dV takes P.m and dS = P (m dP - delta)
+          float mk = 1.f;
+          if (a.drop.thr)
+            mk = drop_val(a.drop, ((static_cast<unsigned long long>(b) * p.H + h) * Tn + t0 + qi) * S + key0 + kk, 1.f);
+          Ps[qi * 33 + kk] = pr * mk;
+          dSs[qi * 33 + kk] = pr * (mk * dp[e] - dl);
         }
       }
       __syncthreads();
@@ -253,6 +258,7 @@ int xattn_bwd(const XattnBwd* p, cudaStream_t st) {
   a.f = p->f;
   a.scratch = p->scratch;
   a.f.weights = nullptr;
+  a.drop = make_drop(p->f.drop);
   a.dout = p->dout; a.dq = p->dq; a.dk = p->dk; a.dv = p->dv;
   const int D = p->f.D;
   const size_t smem = (4 * static_cast<size_t>(kT) * (D + 1) + 2 * kT * 33 + 2 * static_cast<size_t>(p->f.T)) * 4;

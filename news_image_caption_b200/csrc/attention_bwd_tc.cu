@@ -43,6 +43,7 @@ struct Args {
   int B, T, S, H, mask_S;
   float scale, scale_log2e;
   int n_items, n_qt, n_tiles;
+  DropSpec drop;                                  // the forward's dropout on the probabilities
 };
 
 struct Bars {
@@ -250,10 +251,20 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         uint32_t pk[16], dk[16];
 #pragma unroll
         for (int c = 0; c < 32; c += 2) {
-          const float p0 = ok ? exp2f(fmaf(__uint_as_float(sv[c]), a.scale_log2e, -lse2[c])) : 0.f;
-          const float p1 = ok ? exp2f(fmaf(__uint_as_float(sv[c + 1]), a.scale_log2e, -lse2[c + 1])) : 0.f;
-          const float d0 = p0 * (__uint_as_float(dv[c]) - dl[c]) * a.scale;
-          const float d1 = p1 * (__uint_as_float(dv[c + 1]) - dl[c + 1]) * a.scale;
+          float p0 = ok ? exp2f(fmaf(__uint_as_float(sv[c]), a.scale_log2e, -lse2[c])) : 0.f;
+          float p1 = ok ? exp2f(fmaf(__uint_as_float(sv[c + 1]), a.scale_log2e, -lse2[c + 1])) : 0.f;
+          // with dropout m (0 or 1/(1-p)): dV uses P.m, dS = scale * P * (m * dP - delta)
+          float m0 = 1.f, m1 = 1.f;
+          if (a.drop.thr) {
+            const unsigned long long i0 =
+                ((static_cast<unsigned long long>(b) * a.H + hp * 2 + hd) * a.T + j * TQ + c) * a.S + i * TKEYS + quad * 32 + lane;
+            m0 = drop_val(a.drop, i0, 1.f);
+            m1 = drop_val(a.drop, i0 + a.S, 1.f);
+          }
+          const float d0 = p0 * (m0 * __uint_as_float(dv[c]) - dl[c]) * a.scale;
+          const float d1 = p1 * (m1 * __uint_as_float(dv[c + 1]) - dl[c + 1]) * a.scale;
+          p0 *= m0;
+          p1 *= m1;
           pk[c >> 1] = pack_bf16x2(p0, p1);
           dk[c >> 1] = pack_bf16x2(d0, d1);
         }
@@ -385,6 +396,7 @@ int xattn_bwd_tc(const XattnBwd* p, cudaStream_t st) {
   a.mask = f.mask_mode == TNT_MASK_KEY_PADDING ? f.mask : nullptr;
   a.m_stride_b = f.m_stride_b;
   a.lse = f.lse; a.delta = p->scratch;
+  a.drop = make_drop(f.drop);
   a.dq = p->dq; a.q_stride_t = f.q_stride_t; a.q_stride_b = f.q_stride_b;
   a.dk = p->dk; a.dv = p->dv; a.k_stride_s = f.k_stride_s; a.k_stride_b = f.k_stride_b;
   a.B = f.B; a.T = f.T; a.S = f.S; a.H = f.H;

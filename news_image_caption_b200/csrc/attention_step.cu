@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(const __grid_co
 int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st);
 
 bool xattn_step_supported(const tnt_xattn_params* p) {
-  if (p->T != 1 || p->dtype != TNT_BF16 || p->D != 64 || (p->H % kHeadsPerCta) != 0 || p->n_extra != 0 || p->weights)
+  if (p->T != 1 || p->dtype != TNT_BF16 || p->D != 64 || (p->H % kHeadsPerCta) != 0 || p->n_extra != 0 || p->weights || p->drop.p > 0.f)
     return false;
   if (p->mask_mode != TNT_MASK_NONE && p->mask_mode != TNT_MASK_KEY_PADDING) return false;
   const long strides = p->q_stride_b | p->k_stride_s | p->k_stride_b | p->v_stride_s | p->v_stride_b | p->o_stride_b;

@@ -41,6 +41,7 @@ struct Args {
   int B, T, S, H, mask_S;
   float scale_log2e;
   int n_items, n_qt, n_tiles;
+  DropSpec drop;                                  // dropout on the probabilities (the normaliser stays un-dropped)
 };
 
 struct Bars {
@@ -246,6 +247,12 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           float p1 = ok ? exp2f(fmaf(__uint_as_float(v[c + 1]), a.scale_log2e, -mx[c + 1])) : 0.f;
           ls[c] += p0;
           ls[c + 1] += p1;
+          if (a.drop.thr) {
+            const unsigned long long i0 =
+                ((static_cast<unsigned long long>(b) * a.H + hp * 2 + hd) * a.T + qt * TQ + c) * a.S + i * TKEYS + quad * 32 + lane;
+            p0 = drop_val(a.drop, i0, p0);
+            p1 = drop_val(a.drop, i0 + a.S, p1);
+          }
           pk[c >> 1] = pack_bf16x2(p0, p1);
         }
         ptx::mbar_wait(&bar->p_empty[ps], pph ^ 1);
@@ -330,6 +337,7 @@ int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st) {
   a.mask_S = p->mask_S > 0 ? p->mask_S : p->S;
   a.scale_log2e = p->scale * 1.4426950408889634f;
   a.lse = p->lse; a.scale = p->scale;
+  a.drop = make_drop(p->drop);
   a.n_qt = (p->T + atc::TQ - 1) / atc::TQ;
   a.n_items = p->B * (p->H / 2) * a.n_qt;
   a.n_tiles = (p->S + atc::TKEYS - 1) / atc::TKEYS;

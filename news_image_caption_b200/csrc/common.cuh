@@ -100,8 +100,50 @@ inline int num_sms() {
 }
 inline cudaStream_t as_stream(tnt_stream s) { return reinterpret_cast<cudaStream_t>(s); }
 
+// ------------------------------------------------------------------ counter-based dropout (tnt_dropout)
+// keep(index) = drop_bits(k0, k1, index) >= thr; (k0, k1) fold the seed and the site.  thr == 0: site off.
+struct DropSpec {
+  uint32_t thr = 0;
+  float scale = 1.f;
+  uint32_t k0 = 0, k1 = 0;
+  long ld = 0, gs = 0;
+};
+__host__ __device__ __forceinline__ uint32_t drop_bits(uint32_t k0, uint32_t k1, unsigned long long idx) {
+  uint32_t h = k0 ^ static_cast<uint32_t>(idx);
+  h *= 0x9E3779B1u;
+  h ^= h >> 16;
+  h += k1 + static_cast<uint32_t>(idx >> 32) * 0x85EBCA6Bu;
+  h ^= h >> 15;
+  h *= 0x2C1B3C6Du;
+  h ^= h >> 12;
+  h *= 0x297A2D39u;
+  h ^= h >> 15;
+  return h;
+}
+inline void drop_keys(uint64_t seed, uint32_t site, uint32_t* k0, uint32_t* k1) {
+  *k0 = static_cast<uint32_t>(seed) * 0x9E3779B1u + site * 0x7FEB352Du + 0x165667B1u;
+  *k1 = static_cast<uint32_t>(seed >> 32) ^ (site * 0x846CA68Bu + 0x27D4EB2Fu);
+}
+inline DropSpec make_drop(const tnt_dropout& d) {
+  DropSpec s;
+  if (!(d.p > 0.f)) return s;
+  const double t = static_cast<double>(d.p) * 4294967296.0;
+  s.thr = t >= 4294967295.0 ? 0xFFFFFFFFu : static_cast<uint32_t>(t);
+  if (s.thr == 0) s.thr = 1;
+  s.scale = d.p < 1.f ? 1.f / (1.f - d.p) : 0.f;
+  drop_keys(d.seed, d.site, &s.k0, &s.k1);
+  s.ld = d.ld;
+  s.gs = d.group_stride;
+  return s;
+}
+
 // ------------------------------------------------------------------ device side
 using bf16 = __nv_bfloat16;
+
+// value after dropout: scaled when kept, 0 when dropped
+__device__ __forceinline__ float drop_val(const DropSpec& s, unsigned long long idx, float v) {
+  return drop_bits(s.k0, s.k1, idx) >= s.thr ? v * s.scale : 0.f;
+}
 
 // PDL: block until the preceding kernel of the stream has completed and its writes are visible (no-op for a plain
 // launch), then let the NEXT kernel's CTAs be scheduled as soon as SM resources free up.

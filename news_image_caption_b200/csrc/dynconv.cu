@@ -43,7 +43,12 @@ __device__ __forceinline__ void stage_tap_logits(const T* lg, long ldl, int B, i
     taps[r * HG * K + rem] = (t0 + r < T_end) ? to_f(lg[(static_cast<long>(t0 + r) * B + b) * ldl + h0 * K + rem]) : 0.f;
   }
 }
-__device__ __forceinline__ void normalise_taps(int t0, int T_end, int rows, int hg, int HG, int K, float* taps) {
+// Tap dropout (weight_dropout, dynamic.py:305; element index ((t*B + b)*H + h)*K + j): the forward stores the dropped
+// taps (w / (1-p) or 0); the backward keeps w and marks dropped taps with the SIGN bit (w >= 0), because the soft-max
+// backward needs every un-dropped w while the value path and d(taps) need the mask.
+__device__ __forceinline__ void normalise_taps(int t0, int T_end, int rows, int hg, int HG, int K, float* taps,
+                                               const DropSpec& dr = DropSpec(), int B = 0, int b = 0, int H = 0, int h0 = 0,
+                                               bool sign_encode = false) {
   for (int i = threadIdx.x; i < rows * hg; i += kThreads) {
     const int r = i / hg, hl = i - r * hg;
     if (t0 + r >= T_end) continue;
@@ -57,8 +62,20 @@ __device__ __forceinline__ void normalise_taps(int t0, int T_end, int rows, int 
       s += e;
     }
     const float inv = 1.f / s;
-    for (int j = 0; j < K; ++j) o[j] *= inv;
+    if (!dr.thr) {
+      for (int j = 0; j < K; ++j) o[j] *= inv;
+    } else {
+      const unsigned long long i0 = ((static_cast<unsigned long long>(t0 + r) * B + b) * H + h0 + hl) * K;
+      for (int j = 0; j < K; ++j) {
+        const float w = o[j] * inv;
+        const bool keep = drop_bits(dr.k0, dr.k1, i0 + j) >= dr.thr;
+        o[j] = sign_encode ? (keep ? w : -w) : (keep ? w * dr.scale : 0.f);
+      }
+    }
   }
+}
+__device__ __forceinline__ float tap_kept(float enc, float scale) {      // sign-encoded tap -> dropped-out value
+  return (__float_as_uint(enc) >> 31) ? 0.f : enc * scale;
 }
 
 // ------------------------------------------------------------------------------ forward
@@ -82,7 +99,7 @@ __device__ __forceinline__ void zero8(T* dst) {
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_params p, int CC, int HG) {
+__global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_params p, int CC, int HG, DropSpec dr) {
   pdl_wait();
   extern __shared__ float sm[];
   const int K = p.K, R = p.C / p.H, B = p.B;
@@ -111,7 +128,7 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_param
   const int hg = cc / R, h0 = c0 / R;
   stage_tap_logits(lg, p.ldl, B, b, t0, p.T, TT, hg, HG, K, h0, taps);
   __syncthreads();
-  normalise_taps(t0, p.T, TT, hg, HG, K, taps);
+  normalise_taps(t0, p.T, TT, hg, HG, K, taps, dr, B, b, p.H, h0, false);
   __syncthreads();
   const int ngrp = (TT + kNT - 1) / kNT;
   for (int i = threadIdx.x; i < ngrp * nv; i += kThreads) {
@@ -185,7 +202,7 @@ __global__ void __launch_bounds__(kThreads) dynconv_step_kernel(tnt_dynconv_step
 // smem: xs [(TT+K-1)][CCP] (inputs t0-(K-1) .. t0+TT-1), dys [(TT+K-1)][CCP] (grads t0 .. t0+TT+K-2),
 //       taps [(TT+K-1)][HG][K] for t0 .. t0+TT+K-2, dws [TT][HG][K]; CCP = CC + 1 (bank spread).
 template <typename T>
-__global__ void __launch_bounds__(kThreads) dynconv_bwd_kernel(tnt_dynconv_bwd_params p, int CC, int HG) {
+__global__ void __launch_bounds__(kThreads) dynconv_bwd_kernel(tnt_dynconv_bwd_params p, int CC, int HG, DropSpec dr) {
   extern __shared__ float sm[];
   const int K = p.K, R = p.C / p.H, B = p.B, KM = K - 1;
   const int b = blockIdx.x, c0 = blockIdx.y * CC, t0 = blockIdx.z * kTT;
@@ -226,8 +243,9 @@ __global__ void __launch_bounds__(kThreads) dynconv_bwd_kernel(tnt_dynconv_bwd_p
   }
   stage_tap_logits(lg, p.ldl, B, b, t0, p.T, rows, hg, HG, K, h0, taps);
   __syncthreads();
-  normalise_taps(t0, p.T, rows, hg, HG, K, taps);
+  normalise_taps(t0, p.T, rows, hg, HG, K, taps, dr, B, b, p.H, h0, true);      // dropped taps carry the sign bit
   __syncthreads();
+  const float dscale = dr.thr ? dr.scale : 1.f;
 
   // dx[ts] = sum_j w[ts+KM-j][j] * dy[ts+KM-j]   (value path)
   T* dx = reinterpret_cast<T*>(p.dx);
@@ -237,7 +255,7 @@ __global__ void __launch_bounds__(kThreads) dynconv_bwd_kernel(tnt_dynconv_bwd_p
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int j = 0; j < K; ++j) {
       const int r = t + KM - j;                     // local row of the consuming timestep
-      const float wj = taps[(r * HG + hl) * K + j];
+      const float wj = tap_kept(taps[(r * HG + hl) * K + j], dscale);
       const float* d = dys + r * CCP + vc * 8;
 #pragma unroll
       for (int e = 0; e < 8; ++e) acc[e] = fmaf(wj, d[e], acc[e]);
@@ -254,7 +272,7 @@ __global__ void __launch_bounds__(kThreads) dynconv_bwd_kernel(tnt_dynconv_bwd_p
         const float* xr = xs + (t + j) * CCP + hl * R;     // local row of input t-KM+j is t+j
         const float* d = dys + t * CCP + hl * R;
         for (int r = 0; r < R; ++r) s = fmaf(d[r], xr[r], s);
-        dws[(t * HG + hl) * K + j] = s;
+        dws[(t * HG + hl) * K + j] = (__float_as_uint(taps[(t * HG + hl) * K + j]) >> 31) ? 0.f : s * dscale;
       }
     }
     __syncwarp();
@@ -262,10 +280,10 @@ __global__ void __launch_bounds__(kThreads) dynconv_bwd_kernel(tnt_dynconv_bwd_p
     const float* w = taps + (t * HG + hl) * K;
     const float* dwp = dws + (t * HG + hl) * K;
     float dot = 0.f;
-    for (int j = lane; j < K; j += 32) dot = fmaf(w[j], dwp[j], dot);
+    for (int j = lane; j < K; j += 32) dot = fmaf(fabsf(w[j]), dwp[j], dot);
     dot = warp_sum(dot);
     T* dl = reinterpret_cast<T*>(p.dlogits) + (static_cast<long>(t0 + t) * B + b) * p.lddl + (h0 + hl) * K;
-    for (int j = lane; j < K; j += 32) dl[j] = from_f<T>(w[j] * (dwp[j] - dot));
+    for (int j = lane; j < K; j += 32) dl[j] = from_f<T>(fabsf(w[j]) * (dwp[j] - dot));
   }
 }
 
@@ -314,12 +332,14 @@ extern "C" int tnt_dynconv_fwd(const tnt_dynconv_params* p, tnt_stream stream) {
   const int ngroups = pick_group(p->C, p->H, 256, &CC, &HG);
   const size_t smem = static_cast<size_t>(kTT + p->K - 1) * CC * dtype_size(p->dtype) + static_cast<size_t>(kTT) * HG * p->K * 4;
   dim3 grid(p->B, ngroups, (p->T + kTT - 1) / kTT);
+  TNT_CHECK_ARG(p->drop.p >= 0.f && p->drop.p < 1.f, "dynconv: dropout p = %f", p->drop.p);
+  const DropSpec dr = make_drop(p->drop);
   if (p->dtype == TNT_BF16) {
     TNT_TRY(set_smem(dynconv_fwd_kernel<bf16>, smem));
-    TNT_CUDA(launch_pdl(dynconv_fwd_kernel<bf16>, grid, dim3(kThreads), smem, as_stream(stream), 1, *p, CC, HG));
+    TNT_CUDA(launch_pdl(dynconv_fwd_kernel<bf16>, grid, dim3(kThreads), smem, as_stream(stream), 1, *p, CC, HG, dr));
   } else {
     TNT_TRY(set_smem(dynconv_fwd_kernel<float>, smem));
-    TNT_CUDA(launch_pdl(dynconv_fwd_kernel<float>, grid, dim3(kThreads), smem, as_stream(stream), 1, *p, CC, HG));
+    TNT_CUDA(launch_pdl(dynconv_fwd_kernel<float>, grid, dim3(kThreads), smem, as_stream(stream), 1, *p, CC, HG, dr));
   }
   TNT_LAUNCHED();
   return TNT_OK;
@@ -353,12 +373,14 @@ extern "C" int tnt_dynconv_bwd(const tnt_dynconv_bwd_params* p, tnt_stream strea
   const size_t smem = (2 * static_cast<size_t>(rows) * (CC + 1) + static_cast<size_t>(rows) * HG * p->K +
                        static_cast<size_t>(kTT) * HG * p->K) * 4;
   dim3 grid(p->B, ngroups, (p->T + kTT - 1) / kTT);
+  TNT_CHECK_ARG(p->drop.p >= 0.f && p->drop.p < 1.f, "dynconv_bwd: dropout p = %f", p->drop.p);
+  const DropSpec dr = make_drop(p->drop);
   if (p->dtype == TNT_BF16) {
     TNT_TRY(set_smem(dynconv_bwd_kernel<bf16>, smem));
-    dynconv_bwd_kernel<bf16><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG);
+    dynconv_bwd_kernel<bf16><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG, dr);
   } else {
     TNT_TRY(set_smem(dynconv_bwd_kernel<float>, smem));
-    dynconv_bwd_kernel<float><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG);
+    dynconv_bwd_kernel<float><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG, dr);
   }
   TNT_LAUNCHED();
   return TNT_OK;

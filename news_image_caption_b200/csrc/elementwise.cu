@@ -433,3 +433,68 @@ extern "C" int tnt_cast(const void* src, void* dst, int64_t n, int dtype_src, in
   TNT_LAUNCHED();
   return TNT_OK;
 }
+
+// ------------------------------------------------------------------------------ dropout (counter based)
+namespace tnt {
+namespace {
+// out[r, c] = dropout(in[r, c]) (+ res[r, c]); 8 columns per thread (cols % 8 == 0), index = r * ld_idx + c
+template <typename T>
+__global__ void __launch_bounds__(256) dropout_kernel(const T* in, long ldi, const T* res, long ldr, T* out, long ldo, int rows,
+                                                     int cols, DropSpec d) {
+  const int nv = cols >> 3;
+  const long n = static_cast<long>(rows) * nv;
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < n; i += gridDim.x * 256L) {
+    const long r = i / nv;
+    const int c = static_cast<int>(i - r * nv) * 8;
+    float v[8];
+    load8(in + r * ldi + c, v);
+    const unsigned long long i0 = static_cast<unsigned long long>(r) * d.ld + c;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = drop_val(d, i0 + j, v[j]);
+    if (res) {
+      float t[8];
+      load8(res + r * ldr + c, t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += t[j];
+    }
+    store8(out + r * ldo + c, v);
+  }
+}
+}  // namespace
+
+int dropout_apply(const void* in, long ldi, const void* res, long ldr, void* out, long ldo, int rows, int cols, int dtype,
+                  const tnt_dropout& dr, cudaStream_t st) {
+  TNT_CHECK_ARG(in && out && rows >= 0 && cols > 0 && cols % 8 == 0, "dropout: bad arguments (cols must be a multiple of 8)");
+  TNT_CHECK_ARG(dr.p >= 0.f && dr.p < 1.f, "dropout: p = %f", dr.p);
+  const size_t E = dtype_size(dtype);
+  TNT_CHECK_ALIGN(aligned16(in) && aligned16(out) && (!res || aligned16(res)) && (ldi * E) % 16 == 0 && (ldo * E) % 16 == 0 &&
+                      (!res || (ldr * E) % 16 == 0),
+                  "dropout: rows must be 16-byte aligned");
+  if (rows == 0) return TNT_OK;
+  DropSpec d = make_drop(dr);
+  if (d.ld == 0) d.ld = cols;
+  if (!d.thr) { d.thr = 0; d.scale = 1.f; }             // p == 0: plain copy (+ residual); drop_bits >= 0 always keeps
+  const long n = static_cast<long>(rows) * (cols / 8);
+  const int grid = static_cast<int>(std::min<long>((n + 255) / 256, 8L * num_sms()));
+  if (dtype == TNT_BF16)
+    dropout_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<const bf16*>(in), ldi, static_cast<const bf16*>(res), ldr,
+                                               static_cast<bf16*>(out), ldo, rows, cols, d);
+  else
+    dropout_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(in), ldi, static_cast<const float*>(res), ldr,
+                                                static_cast<float*>(out), ldo, rows, cols, d);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+}  // namespace tnt
+
+extern "C" uint32_t tnt_dropout_bits(uint64_t seed, uint32_t site, uint64_t index) {
+  uint32_t k0, k1;
+  tnt::drop_keys(seed, site, &k0, &k1);
+  return tnt::drop_bits(k0, k1, index);
+}
+
+extern "C" int tnt_dropout_apply(const void* in, int64_t ldi, const void* residual, int64_t ldr, void* out, int64_t ldo,
+                                 int rows, int cols, int dtype, const tnt_dropout* d, tnt_stream stream) {
+  TNT_CHECK_ARG(d, "dropout: null descriptor");
+  return tnt::dropout_apply(in, ldi, residual, ldr, out, ldo, rows, cols, dtype, *d, tnt::as_stream(stream));
+}

@@ -58,6 +58,8 @@ struct tnt_decoder {
   std::vector<cudaEvent_t> stage_events;   // training: gradients of stage i are final (tnt_decoder_stream_wait_stage)
   std::map<std::string, float*> grads; // training: fp32 gradient buffer per state_dict key (tnt_decoder_set_grad)
   int article_idx = -1;
+  tnt_dropout_config drop_cfg = {};    // training dropout (tnt_decoder_set_dropout); all zero = off
+  uint64_t drop_step = 0;              // training steps issued since the configuration was set
   // pipelined host scoring (tnt_decoder_score_host_submit / _wait): copy stream + per-slot events
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_h2d[2] = {}, ev_free[2] = {}, ev_done[2] = {};
@@ -80,6 +82,7 @@ namespace tnt {
 struct FwdWs {
   void *X0, *X1, *h, *logits, *cbuf, *ybuf, *Q, *AO, *CAT, *F;
   void *ybuf2, *CATln;     // inference: aliases of ybuf / CAT; training keeps the pre-LayerNorm tensors
+  void* Xd;                // training with input_dropout: the dropped-out layer input linear1 reads (else NULL)
   void* kv[TNT_MAX_SOURCES];
   float* lse[TNT_MAX_SOURCES];   // training: attention log-sum-exp [B, H, T] per source (NULL: not saved)
   size_t total;
@@ -91,7 +94,18 @@ int embed(tnt_decoder* d, const int64_t* ids, int B, int T, void* out, const int
 int project_kv(tnt_decoder* d, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st);
 // one decoder layer on N = T*B rows; `ring`/`pos` != NULL selects the single-step conv (T must be 1)
 int run_layer(tnt_decoder* d, int l, const tnt_contexts* ctx, const FwdWs& w, const void* Xin, void* Xout, int B, int T,
-              void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st, int kv_group = 1);
+              void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st, int kv_group = 1,
+              const tnt_dropout_config* dr = nullptr);
+// dr != NULL (training): the dropout sites of the layer are active with seed dr->seed (include/tnt_b200.h, TNT_DROP_SITE)
+int dropout_apply(const void* in, long ldi, const void* res, long ldr, void* out, long ldo, int rows, int cols, int dtype,
+                  const tnt_dropout& dr, cudaStream_t st);
+inline tnt_dropout drop_site(const tnt_dropout_config* dr, float p, uint32_t site, long ld = 0, long gs = 0) {
+  tnt_dropout t = {};
+  if (dr && p > 0.f) {
+    t.p = p; t.site = site; t.seed = dr->seed; t.ld = ld; t.group_stride = gs;
+  }
+  return t;
+}
 // kv_group > 1 (beam search): B counts beam rows; rows b*kv_group.. share context entry b (ctx->B = B / kv_group)
 
 }  // namespace tnt

@@ -18,13 +18,15 @@ inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
 
 int linear(const void* a, long lda, const void* w, long ldw, const float* bias, void* c, long ldc, int M, int N, int K,
            int dtype, int epi, const void* res, long ldr, cudaStream_t st, int groups = 1, long sa = 0, long sw = 0,
-           long sb = 0, long sr = 0, long sc = 0, const void* pf = nullptr, size_t pf_bytes = 0) {
+           long sb = 0, long sr = 0, long sc = 0, const void* pf = nullptr, size_t pf_bytes = 0,
+           const tnt_dropout* drop = nullptr) {
   tnt_linear_params p = {};
   p.a = a; p.lda = lda; p.w = w; p.ldw = ldw; p.bias = bias; p.residual = res; p.ldr = ldr; p.c = c; p.ldc = ldc;
   p.M = M; p.N = N; p.K = K; p.groups = groups;
   p.stride_a = sa; p.stride_w = sw; p.stride_bias = sb; p.stride_res = sr; p.stride_c = sc;
   p.dtype_in = dtype; p.dtype_out = dtype; p.epilogue = epi;
   p.prefetch = pf; p.prefetch_bytes = pf_bytes;
+  if (drop) p.drop = *drop;
   return launch_gemm(&p, -1, nullptr, nullptr, st);
 }
 
@@ -98,7 +100,8 @@ int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStre
 }
 
 int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, const void* Xin, void* Xout, int B, int T,
-              void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st, int kv_group) {
+              void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st, int kv_group,
+              const tnt_dropout_config* dr) {
   const tnt_decoder_config& c = D->cfg;
   const LayerW& L = D->layers[l];
   const int d = c.d, ns = c.n_sources, N = B * T, H = c.heads, dt = c.dtype;
@@ -110,7 +113,18 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
   const size_t dd = static_cast<size_t>(d) * d * E;
   const void* next_w1 = l + 1 < c.n_layers ? D->layers[l + 1].w1 : D->ada.head_w;
   const size_t next_w1_bytes = l + 1 < c.n_layers ? 2 * dd : static_cast<size_t>(D->ada.cuts.cut[0] + D->ada.cuts.n - 1) * d * E;
-  TNT_TRY(linear(Xin, d, L.w1, d, L.b1, w.h, d, N, 2 * d, d, dt, EPI_GLU, nullptr, 0, st, 1, 0, 0, 0, 0, 0, L.wtap,
+  // dropout sites of the layer (training only; decoder_flattened.py:283,289,308,326,340,342)
+  const tnt_dropout d_conv = drop_site(dr, dr ? dr->dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_CONV_OUT));
+  const tnt_dropout d_attn = drop_site(dr, dr ? dr->dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_ATTN_OUT), static_cast<long>(ns) * d, d);
+  const tnt_dropout d_ffn = drop_site(dr, dr ? dr->dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_FFN_OUT));
+  const tnt_dropout d_relu = drop_site(dr, dr ? dr->relu_dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_RELU));
+  const void* X1in = Xin;                 // what linear1 reads: the layer input after input_dropout
+  if (dr && dr->input_dropout > 0.f) {
+    TNT_CHECK_ARG(w.Xd, "decoder: input_dropout needs the training workspace");
+    TNT_TRY(dropout_apply(Xin, d, nullptr, 0, w.Xd, d, N, d, dt, drop_site(dr, dr->input_dropout, TNT_DROP_SITE(l, TNT_DROP_INPUT)), st));
+    X1in = w.Xd;
+  }
+  TNT_TRY(linear(X1in, d, L.w1, d, L.b1, w.h, d, N, 2 * d, d, dt, EPI_GLU, nullptr, 0, st, 1, 0, 0, 0, 0, 0, L.wtap,
                  static_cast<size_t>(H) * L.K * d * E));
   TNT_TRY(linear(w.h, d, L.wtap, d, nullptr, w.logits, ldl, N, H * L.K, d, dt, EPI_NONE, nullptr, 0, st, 1, 0, 0, 0, 0, 0, L.w2, dd));
   if (ring || pos) {
@@ -123,9 +137,10 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     tnt_dynconv_params cp = {};
     cp.x = w.h; cp.ldx = d; cp.logits = w.logits; cp.ldl = ldl; cp.y = w.cbuf; cp.ldy = d;
     cp.T = T; cp.B = B; cp.C = d; cp.H = H; cp.K = L.K; cp.dtype = dt;
+    cp.drop = drop_site(dr, dr ? dr->weight_dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_TAPS));
     TNT_TRY(tnt_dynconv_fwd(&cp, st));
   }
-  TNT_TRY(linear(w.cbuf, d, L.w2, d, L.b2, w.ybuf, d, N, d, d, dt, EPI_RESIDUAL, Xin, d, st, 1, 0, 0, 0, 0, 0, L.wq, ns * dd));
+  TNT_TRY(linear(w.cbuf, d, L.w2, d, L.b2, w.ybuf, d, N, d, d, dt, EPI_RESIDUAL, Xin, d, st, 1, 0, 0, 0, 0, 0, L.wq, ns * dd, &d_conv));
   TNT_TRY(layernorm(w.ybuf, w.X1, d, L.ln_conv_g, L.ln_conv_b, N, d, 1, dt, 0, 0, st));
   // multi-source cross attention: one stacked query projection, per-source attention, grouped out-proj
   TNT_TRY(linear(w.X1, d, L.wq, d, L.bq, w.Q, static_cast<long>(ns) * d, N, ns * d, d, dt, EPI_NONE, nullptr, 0, st, 1, 0, 0, 0, 0, 0,
@@ -152,6 +167,7 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     ap.B = B; ap.T = T; ap.S = ctx->S[s] + 2; ap.H = H; ap.D = d / H; ap.n_extra = 0;
     ap.mask_S = ctx->S[s];
     ap.kv_group = kv_group;
+    ap.drop = drop_site(dr, dr ? dr->attention_dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_ATTN_PROB + s));
     if (ctx->S[s] == 0) ap.mask_mode = TNT_MASK_NONE;
     ap.scale = 1.0f / sqrtf(static_cast<float>(d / H));
     ap.dtype = dt;
@@ -176,15 +192,15 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     }
   }
   TNT_TRY(linear(w.AO, static_cast<long>(ns) * d, L.wo, d, L.bo, w.CAT, static_cast<long>(ns) * d, N, d, d, dt, EPI_RESIDUAL,
-                 w.X1, d, st, ns, d, static_cast<long>(d) * d, d, 0, d, L.wc, ns * dd));
+                 w.X1, d, st, ns, d, static_cast<long>(d) * d, d, 0, d, L.wc, ns * dd, &d_attn));
   TNT_TRY(layernorm(w.CAT, w.CATln, d, L.ln_src_g, L.ln_src_b, N * ns, d, ns, dt, 0, 0, st));
   TNT_TRY(linear(w.CATln, static_cast<long>(ns) * d, L.wc, static_cast<long>(ns) * d, L.bc, w.X0, d, N, d, ns * d, dt, EPI_NONE,
                  nullptr, 0, st, 1, 0, 0, 0, 0, 0, L.wf1, static_cast<size_t>(c.ffn) * d * E));
   // feed-forward
   TNT_TRY(linear(w.X0, d, L.wf1, d, L.bf1, w.F, c.ffn, N, c.ffn, d, dt, EPI_RELU, nullptr, 0, st, 1, 0, 0, 0, 0, 0, L.wf2,
-                 static_cast<size_t>(c.ffn) * d * E));
+                 static_cast<size_t>(c.ffn) * d * E, &d_relu));
   TNT_TRY(linear(w.F, c.ffn, L.wf2, c.ffn, L.bf2, w.ybuf2, d, N, d, c.ffn, dt, EPI_RESIDUAL, w.X0, d, st, 1, 0, 0, 0, 0, 0, next_w1,
-                 next_w1_bytes));
+                 next_w1_bytes, &d_ffn));
   TNT_TRY(layernorm(w.ybuf2, Xout, d, L.ln_f_g, L.ln_f_b, N, d, 1, dt, transpose_out ? T : 0, transpose_out ? B : 0, st));
   return TNT_OK;
 }

@@ -1,7 +1,8 @@
 // Decoder engine: one training step = teacher-forced forward (activations kept) + AdaptiveLoss + backward
 // through the loss, every decoder layer, the K/V projections and the embedding -- gradients land in the
 // caller's fp32 buffers, one per reference state_dict key (tnt_decoder_set_grad).
-// What is differentiated (dropout p = 0, the parity configuration):
+// Dropout (tnt_decoder_set_dropout) is counter based: the backward recomputes every mask from (seed, site, index).
+// What is differentiated:
 //   DynamicConvDecoderLayer.forward  ttl/tell/models/decoder_flattened.py:271-345, decoder_faces_objects.py:283-393
 //   MultiHeadAttention               ttl/tell/modules/attention/multi_head.py:288-486
 //   GehringLinear weight_norm        ttl/tell/modules/linear.py:7-33
@@ -20,7 +21,7 @@ namespace {
 inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
 
 struct LayerAct {
-  void *h, *logits, *cbuf, *yc, *X1, *Q, *AO, *CATpre, *CATln, *X0, *F, *yf, *Xout;
+  void *h, *logits, *cbuf, *yc, *X1, *Q, *AO, *CATpre, *CATln, *X0, *F, *yf, *Xout, *Xd;
   float* lse[TNT_MAX_SOURCES];
 };
 
@@ -61,7 +62,7 @@ TrainWs carve_train(const tnt_decoder* D, int B, int T, const int* S, void* ws) 
     a.h = take(N * d * E); a.logits = take(N * D->ld_logits(c.kernels[l]) * E); a.cbuf = take(N * d * E);
     a.yc = take(N * d * E); a.X1 = take(N * d * E); a.Q = take(N * ns * d * E); a.AO = take(N * ns * d * E);
     a.CATpre = take(N * ns * d * E); a.CATln = take(N * ns * d * E); a.X0 = take(N * d * E);
-    a.F = take(N * c.ffn * E); a.yf = take(N * d * E); a.Xout = take(N * d * E);
+    a.F = take(N * c.ffn * E); a.yf = take(N * d * E); a.Xout = take(N * d * E); a.Xd = take(N * d * E);
     for (size_t s = 0; s < TNT_MAX_SOURCES; ++s)
       a.lse[s] = s < ns ? static_cast<float*>(take(N * c.heads * sizeof(float))) : nullptr;
   }
@@ -102,6 +103,7 @@ struct Ctx {
   tnt_decoder* D;
   cudaStream_t st;
   int dt;
+  const tnt_dropout_config* dr;     // this step's dropout (seed already advanced) or NULL
   float* grad(const std::string& key) {
     auto it = D->grads.find(key);
     return it == D->grads.end() ? nullptr : it->second;
@@ -115,6 +117,7 @@ struct Ctx {
 int gemm(Ctx& c, int layout, int epi, const void* A, long lda, const void* W, long ldw, void* C, long ldc, int M, int N,
          int K, int dt_out, const void* res = nullptr, long ldr = 0, const int* m_dyn = nullptr, float alpha = 0.f,
          const float* bias = nullptr, int groups = 1, long sa = 0, long sw = 0, long sr = 0, long sc = 0) {
+  // (dropout never rides on a backward GEMM: masked gradients are materialised with dropout_apply)
   tnt_linear_params p = {};
   p.a = A; p.lda = lda; p.w = W; p.ldw = ldw; p.c = C; p.ldc = ldc; p.residual = res; p.ldr = ldr; p.bias = bias;
   p.M = M; p.N = N; p.K = K; p.m_dyn = m_dyn; p.groups = groups;
@@ -164,7 +167,7 @@ FwdWs layer_ws(const TrainWs& w, int l, int ns) {
   FwdWs f = {};
   const LayerAct& a = w.act[l];
   f.X0 = a.X0; f.X1 = a.X1; f.h = a.h; f.logits = a.logits; f.cbuf = a.cbuf; f.ybuf = a.yc; f.ybuf2 = a.yf;
-  f.Q = a.Q; f.AO = a.AO; f.CAT = a.CATpre; f.CATln = a.CATln; f.F = a.F;
+  f.Q = a.Q; f.AO = a.AO; f.CAT = a.CATpre; f.CATln = a.CATln; f.F = a.F; f.Xd = a.Xd;
   for (int s = 0; s < ns; ++s) {
     f.kv[s] = w.kv[s];
     f.lse[s] = a.lse[s];
@@ -172,7 +175,8 @@ FwdWs layer_ws(const TrainWs& w, int l, int ns) {
   return f;
 }
 
-tnt_xattn_params attn_params(const tnt_decoder* D, const tnt_contexts* ctx, const TrainWs& w, int l, int s) {
+tnt_xattn_params attn_params(const tnt_decoder* D, const tnt_contexts* ctx, const TrainWs& w, int l, int s,
+                             const tnt_dropout_config* dr) {
   const tnt_decoder_config& c = D->cfg;
   const int d = c.d, ns = c.n_sources, B = ctx->B, T = ctx->T;
   const size_t E = D->esz();
@@ -194,6 +198,7 @@ tnt_xattn_params attn_params(const tnt_decoder* D, const tnt_contexts* ctx, cons
   ap.scale = 1.0f / sqrtf(static_cast<float>(d / c.heads));
   ap.dtype = c.dtype;
   ap.lse = a.lse[s];
+  ap.drop = drop_site(dr, dr ? dr->attention_dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_ATTN_PROB + s));
   return ap;
 }
 
@@ -209,13 +214,22 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
   const long nsd = static_cast<long>(ns) * d;
   const size_t E = D->esz();
   const std::string p = "layers." + std::to_string(l) + ".";
-  // ---- final LayerNorm and feed-forward: Xout = LN(yf), yf = fc2(relu(fc1(X0))) + X0
+  const tnt_dropout_config* dr = c.dr;
+  const float p_out = dr ? dr->dropout : 0.f;
+  // ---- final LayerNorm and feed-forward: Xout = LN(yf), yf = drop(fc2(drop_relu(relu(fc1(X0))))) + X0
   TNT_TRY(ln_bwd(c, a.yf, d, w.gA, d, w.gB, d, L.ln_f_g, c.grad(p + "final_layer_norm.weight"),
                  c.grad(p + "final_layer_norm.bias"), N, d));
-  TNT_TRY(gemm(c, TNT_NN, EPI_RELU_BWD, w.gB, d, L.wf2, ffn, w.dF, ffn, N, ffn, d, dt, a.F, ffn));
-  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.gB, d, a.F, ffn, w.dW, ffn, d, ffn, N, TNT_F32));
+  const void* g_ffn = w.gB;                       // gradient w.r.t. the fc2 output (masked copy when dropout is on)
+  if (p_out > 0.f) {
+    TNT_TRY(dropout_apply(w.gB, d, nullptr, 0, w.gD, d, N, d, dt, drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_FFN_OUT)), c.st));
+    g_ffn = w.gD;
+  }
+  // a.F holds the dropped-out ReLU output: F > 0 iff kept and active, and the kept elements carry 1 / (1 - p_relu)
+  const float relu_scale = (dr && dr->relu_dropout > 0.f) ? 1.f / (1.f - dr->relu_dropout) : 0.f;
+  TNT_TRY(gemm(c, TNT_NN, EPI_RELU_BWD, g_ffn, d, L.wf2, ffn, w.dF, ffn, N, ffn, d, dt, a.F, ffn, nullptr, relu_scale));
+  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, g_ffn, d, a.F, ffn, w.dW, ffn, d, ffn, N, TNT_F32));
   TNT_TRY(linear_param_grads(c, p + "fc2.", w.dW, d, ffn, false));
-  TNT_TRY(bias_grad(c, p + "fc2.bias", w.gB, d, N, d, false));
+  TNT_TRY(bias_grad(c, p + "fc2.bias", g_ffn, d, N, d, false));
   TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.dF, ffn, L.wf1, d, w.gC, d, N, d, ffn, dt, w.gB, d));      // gC = dX0
   TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.dF, ffn, a.X0, d, w.dW, d, ffn, d, N, TNT_F32));
   TNT_TRY(linear_param_grads(c, p + "fc1.", w.dW, ffn, d, false));
@@ -231,18 +245,24 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
                    off(w.dCATp, static_cast<size_t>(s) * d, E), nsd, L.ln_src_g + s * d, c.grad(ln + "weight"),
                    c.grad(ln + "bias"), N, d));
   }
-  // ---- per-source attention branch: CATpre_s = out_proj_s(attn_s) + X1
-  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.dCATp, nsd, L.wo, d, w.dAO, nsd, N, d, d, dt, nullptr, 0, nullptr, 0.f, nullptr, ns,
+  // ---- per-source attention branch: CATpre_s = drop(out_proj_s(attn_s)) + X1
+  const void* g_op = w.dCATp;                     // gradient w.r.t. the out_proj outputs [N, ns*d]
+  if (p_out > 0.f) {
+    TNT_TRY(dropout_apply(w.dCATp, nsd, nullptr, 0, w.dCAT, nsd, N, ns * d, dt,
+                          drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_ATTN_OUT), nsd), c.st));
+    g_op = w.dCAT;
+  }
+  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, g_op, nsd, L.wo, d, w.dAO, nsd, N, d, d, dt, nullptr, 0, nullptr, 0.f, nullptr, ns,
                d, static_cast<long>(d) * d, 0, d));
   for (int s = 0; s < ns; ++s) {
     const std::string at = p + "context_attns." + cf.source_names[s] + ".";
     float* dwo = c.grad(at + "out_proj.weight");
     TNT_CHECK_ARG(dwo, "train: gradient buffer for '%sout_proj.weight' missing", at.c_str());
-    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, off(w.dCATp, static_cast<size_t>(s) * d, E), nsd, off(a.AO, static_cast<size_t>(s) * d, E),
+    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, off(g_op, static_cast<size_t>(s) * d, E), nsd, off(a.AO, static_cast<size_t>(s) * d, E),
                  nsd, dwo, d, d, d, N, TNT_F32));
-    TNT_TRY(bias_grad(c, at + "out_proj.bias", off(w.dCATp, static_cast<size_t>(s) * d, E), nsd, N, d, false));
+    TNT_TRY(bias_grad(c, at + "out_proj.bias", off(g_op, static_cast<size_t>(s) * d, E), nsd, N, d, false));
     XattnBwd xb;
-    xb.f = attn_params(D, ctx, w, l, s);
+    xb.f = attn_params(D, ctx, w, l, s, dr);
     xb.dout = off(w.dAO, static_cast<size_t>(s) * d, E);
     xb.dq = off(w.dQ, static_cast<size_t>(s) * d, E);
     xb.dk = off(w.dkv[s], static_cast<size_t>(l) * 2 * d, E);
@@ -262,14 +282,20 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
   // ---- conv block: X1 = LN(yc), yc = linear2(conv(h)) + Xin, h = GLU(linear1(Xin))
   TNT_TRY(ln_bwd(c, a.yc, d, w.gD, d, w.gB, d, L.ln_conv_g, c.grad(p + "conv_layer_norm.weight"),
                  c.grad(p + "conv_layer_norm.bias"), N, d));                                          // gB = dyc
-  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.gB, d, L.w2, d, w.gC, d, N, d, d, dt));                         // gC = dcbuf
-  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.gB, d, a.cbuf, d, w.dW, d, d, d, N, TNT_F32));
+  const void* g_l2 = w.gB;                        // gradient w.r.t. the linear2 output (masked copy when dropout is on)
+  if (p_out > 0.f) {
+    TNT_TRY(dropout_apply(w.gB, d, nullptr, 0, w.gA, d, N, d, dt, drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_CONV_OUT)), c.st));
+    g_l2 = w.gA;
+  }
+  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, g_l2, d, L.w2, d, w.gC, d, N, d, d, dt));                         // gC = dcbuf
+  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, g_l2, d, a.cbuf, d, w.dW, d, d, d, N, TNT_F32));
   TNT_TRY(linear_param_grads(c, p + "linear2.", w.dW, d, d, false));
-  TNT_TRY(bias_grad(c, p + "linear2.bias", w.gB, d, N, d, false));
+  TNT_TRY(bias_grad(c, p + "linear2.bias", g_l2, d, N, d, false));
   {
     tnt_dynconv_bwd_params bp = {};
     bp.x = a.h; bp.ldx = d; bp.logits = a.logits; bp.ldl = ldl; bp.dy = w.gC; bp.lddy = d; bp.dx = w.gD; bp.lddx = d;
     bp.dlogits = w.dlogits; bp.lddl = ldl; bp.T = T; bp.B = B; bp.C = d; bp.H = H; bp.K = L.K; bp.dtype = dt;
+    bp.drop = drop_site(dr, dr ? dr->weight_dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_TAPS));
     TNT_TRY(tnt_dynconv_bwd(&bp, c.st));                                                             // gD = dh (value path)
   }
   {
@@ -278,10 +304,17 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
     TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.dlogits, ldl, a.h, d, dwt, d, HK, d, N, TNT_F32));
   }
   TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.dlogits, ldl, L.wtap, d, w.gC, d, N, d, HK, dt, w.gD, d));   // gC = dh
-  TNT_TRY(gemm(c, TNT_NT, EPI_NONE, Xin, d, L.w1, d, w.raw, 2 * d, N, 2 * d, d, dt, nullptr, 0, nullptr, 0.f, L.b1));
+  const bool in_drop = dr && dr->input_dropout > 0.f;
+  const void* X1in = in_drop ? a.Xd : Xin;        // what linear1 read in the forward
+  TNT_TRY(gemm(c, TNT_NT, EPI_NONE, X1in, d, L.w1, d, w.raw, 2 * d, N, 2 * d, d, dt, nullptr, 0, nullptr, 0.f, L.b1));
   TNT_TRY(glu_bwd(w.raw, 2 * d, w.gC, d, w.draw, 2 * d, N, d, dt, c.st));
-  TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.draw, 2 * d, L.w1, d, w.gA, d, N, d, 2 * d, dt, w.gB, d));    // gA = dXin
-  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.draw, 2 * d, Xin, d, w.dW, d, 2 * d, d, N, TNT_F32));
+  if (in_drop) {                                  // gA = dXin = drop(draw . W1) + dyc
+    TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.draw, 2 * d, L.w1, d, w.gC, d, N, d, 2 * d, dt));
+    TNT_TRY(dropout_apply(w.gC, d, w.gB, d, w.gA, d, N, d, dt, drop_site(dr, dr->input_dropout, TNT_DROP_SITE(l, TNT_DROP_INPUT)), c.st));
+  } else {
+    TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.draw, 2 * d, L.w1, d, w.gA, d, N, d, 2 * d, dt, w.gB, d));    // gA = dXin
+  }
+  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.draw, 2 * d, X1in, d, w.dW, d, 2 * d, d, N, TNT_F32));
   TNT_TRY(linear_param_grads(c, p + "linear1.", w.dW, 2 * d, d, true));
   TNT_TRY(bias_grad(c, p + "linear1.bias", w.draw, 2 * d, N, 2 * d, true));
   return TNT_OK;
@@ -367,6 +400,17 @@ extern "C" size_t tnt_decoder_train_workspace_bytes(const tnt_decoder* d, int B,
   return carve_train(d, B, T, S, nullptr).total;
 }
 
+extern "C" int tnt_decoder_set_dropout(tnt_decoder* d, const tnt_dropout_config* cfg) {
+  TNT_CHECK_ARG(d, "decoder_set_dropout: null decoder");
+  tnt_dropout_config z = {};
+  const tnt_dropout_config& c = cfg ? *cfg : z;
+  const float ps[5] = {c.dropout, c.input_dropout, c.weight_dropout, c.attention_dropout, c.relu_dropout};
+  for (float p : ps) TNT_CHECK_ARG(p >= 0.f && p < 1.f, "decoder_set_dropout: probability %f outside [0, 1)", p);
+  d->drop_cfg = c;
+  d->drop_step = 0;
+  return TNT_OK;
+}
+
 extern "C" int tnt_decoder_set_grad(tnt_decoder* d, const char* key, float* grad) {
   TNT_CHECK_ARG(d && key, "decoder_set_grad: bad arguments");
   if (grad) d->grads[key] = grad;
@@ -390,7 +434,12 @@ extern "C" int tnt_decoder_train_step(tnt_decoder* D, const int64_t* ids, const 
     return TNT_ERR_WORKSPACE;
   }
   cudaStream_t st = as_stream(stream);
-  Ctx c{D, st, cf.dtype};
+  tnt_dropout_config drc = D->drop_cfg;
+  const bool drop_on = drc.dropout > 0.f || drc.input_dropout > 0.f || drc.weight_dropout > 0.f || drc.attention_dropout > 0.f ||
+                       drc.relu_dropout > 0.f;
+  drc.seed += D->drop_step++;
+  const tnt_dropout_config* dr = drop_on ? &drc : nullptr;
+  Ctx c{D, st, cf.dtype, dr};
   while (static_cast<int>(D->stage_events.size()) < Ls + 2) {
     cudaEvent_t e;
     TNT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -402,10 +451,12 @@ extern "C" int tnt_decoder_train_step(tnt_decoder* D, const int64_t* ids, const 
     TNT_TRY(project_kv(D, ctx, f0, st));
   }
   TNT_TRY(embed(D, ids, B, T, w.emb, nullptr, st));
+  const tnt_dropout d_emb = drop_site(dr, dr ? dr->dropout : 0.f, TNT_DROP_SITE_EMBED);     // decoder_flattened.py:109
+  if (d_emb.p > 0.f) TNT_TRY(dropout_apply(w.emb, d, nullptr, 0, w.emb, d, N, d, cf.dtype, d_emb, st));
   for (int l = 0; l < Ls; ++l) {
     FwdWs f = layer_ws(w, l, ns);
     const void* xin = l == 0 ? w.emb : w.act[l - 1].Xout;
-    TNT_TRY(run_layer(D, l, ctx, f, xin, w.act[l].Xout, B, T, nullptr, nullptr, nullptr, false, st));
+    TNT_TRY(run_layer(D, l, ctx, f, xin, w.act[l].Xout, B, T, nullptr, nullptr, nullptr, false, st, 1, dr));
   }
   TNT_TRY(permute_rows(w.act[Ls - 1].Xout, w.Xbt, B, T, d, cf.dtype, false, st));     // T x B -> B x T rows
   TNT_TRY(adasoftmax_nll(D->ada, w.Xbt, d, target, N, cf.pad_idx, out2, w.loss_fwd, w.loss_fwd_bytes, st));
@@ -432,6 +483,7 @@ extern "C" int tnt_decoder_train_step(tnt_decoder* D, const int64_t* ids, const 
     for (int s = 0; s < ns; ++s) TNT_TRY(kv_param_grads(c, ctx, w, l, s));
     TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], st));
   }
+  if (d_emb.p > 0.f) TNT_TRY(dropout_apply(w.gA, d, nullptr, 0, w.gA, d, N, d, cf.dtype, d_emb, st));
   TNT_TRY(embed_bwd(c, ids, B, T, w, w.gA));
   TNT_CUDA(cudaEventRecord(D->stage_events[Ls + 1], st));
   return TNT_OK;

@@ -570,6 +570,12 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
   static const bool pf_on = [] { const char* e = getenv("TNT_L2_PREFETCH"); return !(e && e[0] == '0'); }();
   g.pf = (pf_on && p->prefetch && aligned16(p->prefetch)) ? static_cast<const char*>(p->prefetch) : nullptr;
   g.pf_bytes = g.pf ? (p->prefetch_bytes & ~15ull) : 0;
+  g.drop = make_drop(p->drop);
+  if (g.drop.thr) {
+    TNT_CHECK_ARG(epi == EPI_RESIDUAL || epi == EPI_RELU, "linear: dropout needs the residual or ReLU epilogue");
+    TNT_CHECK_ARG(p->drop.p < 1.f, "linear: dropout p = %f", p->drop.p);
+    if (g.drop.ld == 0) g.drop.ld = p->N;
+  }
   TNT_CHECK_ARG(epi != EPI_SMGRAD || (lse && lse->row_lse && lse->target), "smgrad: missing row statistics");
   TNT_CHECK_ARG(epi != EPI_LSE || (lse && lse->partials && (lse->n_lse >= p->N || lse->side)), "lse: missing buffers");
   const size_t eo = dtype_size(p->dtype_out);

@@ -28,6 +28,8 @@ struct GemmArgs {
   float gscale;
   // L2 prefetch hint (weights of the next GEMM of a chain), issued by the prologue
   const char* pf; unsigned long long pf_bytes;
+  // dropout on the value the RESIDUAL epilogue adds the residual to / on the RELU epilogue's output (thr == 0: off)
+  DropSpec drop;
 };
 
 struct LseExtra {
@@ -98,6 +100,11 @@ __device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m
       if (n0 + i < g.N && !(to_f(rrow[n0 + i]) > 0.f)) acc[i] = 0.f;
   }
   if (EPI == EPI_RESIDUAL) {
+    if (g.drop.thr) {
+      const unsigned long long i0 = static_cast<unsigned long long>(grp) * g.drop.gs + static_cast<unsigned long long>(m) * g.drop.ld + n0;
+#pragma unroll
+      for (int i = 0; i < NC; ++i) acc[i] = drop_val(g.drop, i0 + i, acc[i]);
+    }
     const TOut* rrow = reinterpret_cast<const TOut*>(g.res) + grp * g.sres + static_cast<long>(m) * g.ldr;
     if (NC % 8 == 0 && g.vec_ok && n0 + NC <= g.N) {
 #pragma unroll
@@ -116,6 +123,11 @@ __device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m
   if (EPI == EPI_RELU) {
 #pragma unroll
     for (int i = 0; i < NC; ++i) acc[i] = fmaxf(acc[i], 0.f);
+    if (g.drop.thr) {
+      const unsigned long long i0 = static_cast<unsigned long long>(grp) * g.drop.gs + static_cast<unsigned long long>(m) * g.drop.ld + n0;
+#pragma unroll
+      for (int i = 0; i < NC; ++i) acc[i] = drop_val(g.drop, i0 + i, acc[i]);
+    }
   }
   if (NC % 8 == 0 && g.vec_ok && n0 + NC <= g.N) {
 #pragma unroll

@@ -377,6 +377,16 @@ class DynamicConvDecoder(nn.Module):
         """Call after the optimizer changed the parameters: the prepared (folded, cast) weights are rebuilt."""
         self._dirty = True
 
+    def set_dropout(self, dropout=0.0, input_dropout=0.0, weight_dropout=0.0, attention_dropout=0.0, relu_dropout=0.0,
+                    seed=0):
+        """Dropout of `train_step` (the constructor arguments of DynamicConvDecoder, decoder_flattened.py:24-31;
+        config.yaml:51-69).  Masks are counter based: step k after this call uses seed + k, and every mask bit can
+        be reproduced with ops.dropout_bits(seed + k, site, index).  All zero switches dropout off (parity mode)."""
+        cfg = _lib.DropoutConfig()
+        cfg.dropout, cfg.input_dropout, cfg.weight_dropout = dropout, input_dropout, weight_dropout
+        cfg.attention_dropout, cfg.relu_dropout, cfg.seed = attention_dropout, relu_dropout, int(seed)
+        _lib.check(_lib.lib().tnt_decoder_set_dropout(self._h(), C.byref(cfg)), 'tnt_decoder_set_dropout')
+
     def train_step(self, prev_target, target, contexts, loss_scale=1.0):
         """Forward + AdaptiveLoss + backward.  Gradients of `loss_scale * sum-NLL` are written into `.grad`
         of every parameter (views of `flat_grads`).  Returns a device tensor [loss_sum, n_non_pad]."""

@@ -31,7 +31,37 @@ def _cuda(t):
     return t
 
 
-def linear(a, w, bias=None, epilogue=EPI_NONE, residual=None, out_dtype=None, layout=0, alpha=0.0, m_dyn=None):
+def _drop(spec):
+    """(p, seed, site[, ld, group_stride]) -> tnt_dropout (None: off)."""
+    d = _lib.Dropout()
+    if spec is not None:
+        d.p, d.seed, d.site = float(spec[0]), int(spec[1]), int(spec[2])
+        if len(spec) > 3:
+            d.ld = int(spec[3])
+        if len(spec) > 4:
+            d.group_stride = int(spec[4])
+    return d
+
+
+def dropout_bits(seed, site, index):
+    """Host function: the 32 random bits of element `index` of dropout site `site` (kept iff bits >= p * 2^32)."""
+    return int(_lib.lib().tnt_dropout_bits(int(seed), int(site), int(index)))
+
+
+def dropout(x, p, seed, site, residual=None):
+    """dropout(x) (+ residual) with the counter-based mask of (seed, site); x [rows, cols], index = row * cols + col."""
+    x = _cuda(x).contiguous()
+    x2 = x.view(-1, x.shape[-1])
+    out = torch.empty_like(x2)
+    d = _drop((p, seed, site))
+    r = residual.contiguous().view(-1, x.shape[-1]) if residual is not None else None
+    _lib.check(_lib.lib().tnt_dropout_apply(x2.data_ptr(), x2.shape[1], r.data_ptr() if r is not None else None, x2.shape[1],
+                                            out.data_ptr(), x2.shape[1], x2.shape[0], x2.shape[1], _code(x), C.byref(d), _st()),
+               'tnt_dropout_apply')
+    return out.view(x.shape)
+
+
+def linear(a, w, bias=None, epilogue=EPI_NONE, residual=None, out_dtype=None, layout=0, alpha=0.0, m_dyn=None, drop=None):
     """epilogue(a[M,K] @ w[N,K]^T + bias).  For EPI_GLU `w`/`bias` rows must be pair-interleaved.
     layout 1 (NN): a[M,K] @ w[K,N];  layout 2 (TN): a[K,M]^T @ w[K,N] (weight gradient)."""
     a, w = _cuda(a).contiguous(), _cuda(w).contiguous()
@@ -55,6 +85,7 @@ def linear(a, w, bias=None, epilogue=EPI_NONE, residual=None, out_dtype=None, la
         p.residual, p.ldr = residual.data_ptr(), residual.shape[1]
     p.c, p.ldc, p.M, p.N, p.K, p.groups = c.data_ptr(), n_out, M, N, K, 1
     p.dtype_in, p.dtype_out, p.epilogue = _code(a), _code(c), epilogue
+    p.drop = _drop(drop)
     _lib.check(_lib.lib().tnt_linear_fwd(C.byref(p), _st()), 'tnt_linear_fwd')
     return c
 
@@ -75,7 +106,7 @@ def glu_interleave_bias(b):
     return out
 
 
-def dynconv(x, logits, H, K, hist=None):
+def dynconv(x, logits, H, K, hist=None, drop=None):
     """x [T,B,C], logits [T,B,H*K] -> y [T,B,C]; hist [h,B,C] = previous conv inputs (oldest first)."""
     x, logits = _cuda(x).contiguous(), logits.contiguous()
     T, B, Cc = x.shape
@@ -86,11 +117,12 @@ def dynconv(x, logits, H, K, hist=None):
         hist = hist.contiguous()
         p.hist, p.hist_len = hist.data_ptr(), hist.shape[0]
     p.T, p.B, p.C, p.H, p.K, p.dtype = T, B, Cc, H, K, _code(x)
+    p.drop = _drop(drop)
     _lib.check(_lib.lib().tnt_dynconv_fwd(C.byref(p), _st()), 'tnt_dynconv_fwd')
     return y
 
 
-def dynconv_bwd(x, logits, dy, H, K):
+def dynconv_bwd(x, logits, dy, H, K, drop=None):
     x, logits, dy = _cuda(x).contiguous(), logits.contiguous(), dy.contiguous()
     T, B, Cc = x.shape
     dx, dl = torch.empty_like(x), torch.empty_like(logits)
@@ -98,6 +130,7 @@ def dynconv_bwd(x, logits, dy, H, K):
     p.x, p.ldx, p.logits, p.ldl = x.data_ptr(), Cc, logits.data_ptr(), logits.shape[-1]
     p.dy, p.lddy, p.dx, p.lddx, p.dlogits, p.lddl = dy.data_ptr(), Cc, dx.data_ptr(), Cc, dl.data_ptr(), logits.shape[-1]
     p.T, p.B, p.C, p.H, p.K, p.dtype = T, B, Cc, H, K, _code(x)
+    p.drop = _drop(drop)
     _lib.check(_lib.lib().tnt_dynconv_bwd(C.byref(p), _st()), 'tnt_dynconv_bwd')
     return dx, dl
 
@@ -148,7 +181,7 @@ def layernorm_bwd(x, dy, gamma, eps=1e-5):
 
 
 def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=None, need_weights=False, mask_S=0,
-          lse=None):
+          lse=None, drop=None):
     """q [T,B,E], k/v [S,B,E] (projected) -> out [T,B,E] (+ head-averaged weights [B,T,S+n_extra]).
     pad_mask [B,S] bool True=pad (tell);  v2_mask [B,1|T,S] 'visible' mask (final*), 0 -> -1e9."""
     q, k, v = _cuda(q).contiguous(), k.contiguous(), v.contiguous()
@@ -184,11 +217,12 @@ def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=No
     if lse is not None:
         p.lse = lse.data_ptr()
     p.B, p.T, p.S, p.H, p.D, p.n_extra, p.scale, p.dtype = B, T, S, H, E // H, n_extra, scale, _code(q)
+    p.drop = _drop(drop)
     _lib.check(_lib.lib().tnt_xattn_fwd(C.byref(p), _st()), 'tnt_xattn_fwd')
     return out, w
 
 
-def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=0, lse=None):
+def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=0, lse=None, drop=None):
     """Backward of `xattn` (n_extra = 0: extra rows are ordinary k / v rows).  Returns (dq, dk, dv)."""
     q, k, v, out, dout = [_cuda(t).contiguous() for t in (q, k, v, out, dout)]
     T, B, E = q.shape
@@ -212,6 +246,7 @@ def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=
         p.mask, p.m_stride_b, p.mask_mode = m.data_ptr(), m.shape[1] * S, MASK_V2
         p.m_stride_t = S if m.shape[1] > 1 else 0
     p.B, p.T, p.S, p.H, p.D, p.n_extra, p.scale, p.dtype = B, T, S, H, E // H, 0, scale, _code(q)
+    p.drop = _drop(drop)
     if lse is not None:
         p.lse = lse.data_ptr()
     L = _lib.lib()

@@ -17,10 +17,63 @@ import this module.  The product package never does.
 import math
 from typing import Dict, List, Optional, Sequence
 
+import numpy as np
 import torch
 import torch.nn.functional as F
 
 SD = Dict[str, torch.Tensor]
+
+
+# ----------------------------------------------------------------------------- training dropout
+# The reference draws its dropout masks from torch's RNG (F.dropout).  The CUDA path uses a counter-based generator
+# (include/tnt_b200.h, tnt_dropout_bits) so that the backward can recompute the masks; the functions below restate
+# that generator in numpy so a test can feed the SAME masks to this oracle (and, in the build container, to the
+# unmodified reference through a patched F.dropout: tests/test_oracle_vs_reference.py).
+DROP_INPUT, DROP_TAPS, DROP_CONV_OUT, DROP_ATTN_OUT, DROP_FFN_OUT, DROP_RELU, DROP_ATTN_PROB = range(7)
+DROP_SITE_EMBED = 0xFFFF
+
+
+def dropout_bits(seed: int, site: int, index) -> np.ndarray:
+    """32 random bits per element index (uint32 arithmetic, wrap-around)."""
+    M = np.uint64(0xFFFFFFFF)
+    idx = np.asarray(index, dtype=np.uint64)
+    k0 = ((seed & 0xFFFFFFFF) * 0x9E3779B1 + site * 0x7FEB352D + 0x165667B1) & 0xFFFFFFFF
+    k1 = ((seed >> 32) & 0xFFFFFFFF) ^ ((site * 0x846CA68B + 0x27D4EB2F) & 0xFFFFFFFF)
+    h = np.uint64(k0) ^ (idx & M)
+    h = (h * np.uint64(0x9E3779B1)) & M
+    h ^= h >> np.uint64(16)
+    h = (h + np.uint64(k1) + (((idx >> np.uint64(32)) * np.uint64(0x85EBCA6B)) & M)) & M
+    h ^= h >> np.uint64(15)
+    h = (h * np.uint64(0x2C1B3C6D)) & M
+    h ^= h >> np.uint64(12)
+    h = (h * np.uint64(0x297A2D39)) & M
+    h ^= h >> np.uint64(15)
+    return h.astype(np.uint32)
+
+
+def dropout_mask(p: float, seed: int, site: int, index: torch.Tensor) -> torch.Tensor:
+    """F.dropout's multiplier (0 or 1/(1-p), fp32) for the elements whose counter index is `index`."""
+    p32 = np.float32(p)
+    t = float(p32) * 4294967296.0
+    thr = 0xFFFFFFFF if t >= 4294967295.0 else max(int(t), 1)
+    keep = dropout_bits(seed, site, index.numpy()) >= np.uint32(thr)
+    scale = np.float32(1.0) / (np.float32(1.0) - p32)
+    return torch.from_numpy(keep.astype(np.float32) * scale)
+
+
+class DropoutMasks:
+    """The decoder's dropout configuration (decoder_flattened.py:24-31) with counter-based masks."""
+
+    def __init__(self, dropout=0.0, input_dropout=0.0, weight_dropout=0.0, attention_dropout=0.0, relu_dropout=0.0, seed=0):
+        self.dropout, self.input_dropout, self.weight_dropout = dropout, input_dropout, weight_dropout
+        self.attention_dropout, self.relu_dropout, self.seed = attention_dropout, relu_dropout, seed
+
+    def __call__(self, x: torch.Tensor, p: float, site: int, index: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if p <= 0.0:
+            return x
+        if index is None:
+            index = torch.arange(x.numel()).view(x.shape)
+        return x * dropout_mask(p, self.seed, site, index).to(x.dtype)
 
 
 # ----------------------------------------------------------------------------- linear pieces
@@ -52,7 +105,7 @@ def dynconv_taps(x: torch.Tensor, w_tap: torch.Tensor, H: int, K: int) -> torch.
     return F.softmax(F.linear(x, w_tap).view(T, B, H, K), dim=-1)
 
 
-def dynamic_conv(x: torch.Tensor, w_tap: torch.Tensor, H: int, K: int) -> torch.Tensor:
+def dynamic_conv(x: torch.Tensor, w_tap: torch.Tensor, H: int, K: int, tap_drop=None) -> torch.Tensor:
     """Causal DynamicConv1dTBC (padding_l = K-1, weight_softmax, no renorm, no bias).
 
     y[t,b,h*R+r] = sum_j w[t,b,h,j] * x[t-(K-1)+j, b, h*R+r], x[<0] = 0; the taps that reach
@@ -62,6 +115,8 @@ def dynamic_conv(x: torch.Tensor, w_tap: torch.Tensor, H: int, K: int) -> torch.
     T, B, C = x.shape
     R = C // H
     w = dynconv_taps(x, w_tap, H, K)                      # [T,B,H,K]
+    if tap_drop is not None:                              # weight_dropout on the soft-maxed taps -- dynamic.py:305
+        w = tap_drop(w)
     xp = F.pad(x, (0, 0, 0, 0, K - 1, 0))                 # left-pad time with K-1 zeros
     win = xp.unfold(0, K, 1)                              # [T,B,C,K]; win[t,...,j] = x[t-(K-1)+j]
     y = torch.einsum('tbhrk,tbhk->tbhr', win.reshape(T, B, H, R, K), w)
@@ -108,7 +163,7 @@ def mha_project_kv(mem: torch.Tensor, sd: SD, p: str, E: int):
 
 
 def mha_attend(query: torch.Tensor, k: torch.Tensor, v: torch.Tensor, pad_mask: torch.Tensor,
-               sd: SD, p: str, H: int):
+               sd: SD, p: str, H: int, prob_drop=None):
     """softmax_fp32((Wq x + bq) * d^-1/2 . k^T + mask(-inf)) . v -> out_proj; also the
     head-averaged probabilities [B,T,S+2] -- multi_head.py:348-353, 376-486."""
     T, B, E = query.shape
@@ -123,6 +178,8 @@ def mha_attend(query: torch.Tensor, k: torch.Tensor, v: torch.Tensor, pad_mask: 
     full_mask = torch.cat([pad_mask, pad_mask.new_zeros(B, 2)], 1)   # extra 2 keys never masked
     s = s.masked_fill(full_mask[:, None, None, :], float('-inf'))
     pr = torch.softmax(s.float(), -1).to(s.dtype)
+    if prob_drop is not None:                               # dropout on the probabilities -- multi_head.py:463-464
+        pr = prob_drop(pr)
     o = (pr @ vh).permute(2, 0, 1, 3).reshape(T, B, E)
     out = F.linear(o, sd[p + 'out_proj.weight'], sd[p + 'out_proj.bias'])
     return out, pr.sum(1) / H
@@ -135,22 +192,34 @@ def mha(query, mem, pad_mask, sd: SD, p: str, H: int):
 
 # ----------------------------------------------------------------------------- decoder layer
 def decoder_layer(X: torch.Tensor, contexts: dict, sd: SD, p: str, H: int, K: int,
-                  sources: Sequence[str], conv_hist: Optional[list] = None, kv_cache=None):
+                  sources: Sequence[str], conv_hist: Optional[list] = None, kv_cache=None,
+                  drop: Optional[DropoutMasks] = None, layer: int = 0):
     """DynamicConvDecoderLayer.forward, post-LN (decoder_normalize_before = false) --
     ttl/tell/models/decoder_flattened.py:271-345 (2 sources),
     ttl/tell/models/decoder_faces_objects.py:283-393 (4 sources; concat order image, article,
-    faces, obj).  `conv_hist` is a 1-element list holding the incremental conv buffer."""
+    faces, obj).  `conv_hist` is a 1-element list holding the incremental conv buffer.
+    `drop` (training mode): the F.dropout calls at :283 (input), dynamic.py:305 (taps), :289, :308/:326 (attention
+    outputs), :340 (ReLU), :342, and multi_head.py:463 (probabilities), with the masks of DropoutMasks."""
+    site = lambda kind: layer * 16 + kind
     res = X
+    if drop is not None:
+        X = drop(X, drop.input_dropout, site(DROP_INPUT))
     h = F.glu(gehring_linear(X, sd, p + 'linear1.'), dim=-1)
     w_tap = sd[p + 'conv.weight_linear.weight']
     if conv_hist is None:
-        h = dynamic_conv(h, w_tap, H, K)
+        tap_drop = None if drop is None else (lambda w: drop(w, drop.weight_dropout, site(DROP_TAPS)))
+        h = dynamic_conv(h, w_tap, H, K, tap_drop)
     else:
         h, conv_hist[0] = dynamic_conv_step(h, conv_hist[0], w_tap, H, K)
-    X = layer_norm(res + gehring_linear(h, sd, p + 'linear2.'), sd, p + 'conv_layer_norm.')
+    h = gehring_linear(h, sd, p + 'linear2.')
+    if drop is not None:
+        h = drop(h, drop.dropout, site(DROP_CONV_OUT))
+    X = layer_norm(res + h, sd, p + 'conv_layer_norm.')
 
     outs, attn = [], None
-    for s in sources:
+    Tn, Bn, dm = X.shape
+    ns = len(sources)
+    for si, s in enumerate(sources):
         ap = p + 'context_attns.%s.' % s
         if kv_cache is not None and (p, s) in kv_cache:
             k, v = kv_cache[(p, s)]
@@ -158,17 +227,25 @@ def decoder_layer(X: torch.Tensor, contexts: dict, sd: SD, p: str, H: int, K: in
             k, v = mha_project_kv(contexts[s], sd, ap, X.shape[-1])
             if kv_cache is not None:
                 kv_cache[(p, s)] = (k, v)
-        a, w = mha_attend(X, k, v, contexts[s + '_mask'], sd, ap, H)
+        prob_drop = None if drop is None else (lambda pr, si=si: drop(pr, drop.attention_dropout, site(DROP_ATTN_PROB + si)))
+        a, w = mha_attend(X, k, v, contexts[s + '_mask'], sd, ap, H, prob_drop)
+        if drop is not None:      # element (t, b, c) of source si has counter index (t*B + b)*(ns*d) + si*d + c
+            idx = (torch.arange(Tn * Bn)[:, None] * (ns * dm) + si * dm + torch.arange(dm)[None, :]).view(Tn, Bn, dm)
+            a = drop(a, drop.dropout, site(DROP_ATTN_OUT), idx)
         if s == 'article':
             attn = w
         outs.append(layer_norm(X + a, sd, p + 'context_attn_lns.%s.' % s))
     X = gehring_linear(torch.cat(outs, -1), sd, p + 'context_fc.')
-    f = gehring_linear(F.relu(gehring_linear(X, sd, p + 'fc1.')), sd, p + 'fc2.')
+    f = F.relu(gehring_linear(X, sd, p + 'fc1.'))
+    if drop is not None:
+        f = drop(f, drop.relu_dropout, site(DROP_RELU))
+    f = gehring_linear(f, sd, p + 'fc2.')
+    if drop is not None:
+        f = drop(f, drop.dropout, site(DROP_FFN_OUT))
     X = layer_norm(X + f, sd, p + 'final_layer_norm.')
     return X, attn
 
 
-# ----------------------------------------------------------------------------- embedder
 def sinusoid_table(n: int, d: int, padding_idx: int = 1) -> torch.Tensor:
     """tensor2tensor sinusoids [sin | cos], row `padding_idx` zeroed --
     ttl/tell/modules/token_embedders/positional.py:125-165."""
@@ -293,9 +370,10 @@ def layer_kernel(sd: SD, i: int, H: int) -> int:
 
 
 def decoder_forward(ids: torch.Tensor, contexts: dict, sd: SD, H: int, cutoffs: Sequence[int],
-                    sources: Sequence[str] = ('image', 'article'), state: Optional[dict] = None):
+                    sources: Sequence[str] = ('image', 'article'), state: Optional[dict] = None,
+                    drop: Optional[DropoutMasks] = None):
     """DynamicConvDecoder.forward -- decoder_flattened.py:96-146 / decoder_faces_objects.py:95-144
-    (eval mode: every dropout is the identity).  ids [B,T] -> X [B,T,d], article attn [B,T,S+2].
+    (eval mode: every dropout is the identity; `drop` = training mode with given masks).  ids [B,T] -> X [B,T,d], article attn [B,T,S+2].
     `state` (dict) switches on the incremental path: position offset + per-layer conv buffers
     (+ a K/V cache, which the reference recomputes each step -- same numbers)."""
     start = 0
@@ -303,13 +381,15 @@ def decoder_forward(ids: torch.Tensor, contexts: dict, sd: SD, H: int, cutoffs: 
         start = state.get('pos', 0)
         state['pos'] = start + ids.shape[1]
     X = embed(ids, sd, cutoffs, start).transpose(0, 1)
+    if drop is not None:                                   # decoder_flattened.py:109 (counter index in T x B order)
+        X = drop(X.contiguous(), drop.dropout, DROP_SITE_EMBED)
     attn = None
     for i in range(n_layers(sd)):
         hist = None
         if state is not None:
             hist = state.setdefault(('conv', i), [None])
         X, attn = decoder_layer(X, contexts, sd, 'layers.%d.' % i, H, layer_kernel(sd, i, H),
-                                sources, hist, None if state is None else state.setdefault('kv', {}))
+                                sources, hist, None if state is None else state.setdefault('kv', {}), drop, i)
     return X.transpose(0, 1), attn
 
 

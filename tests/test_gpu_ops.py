@@ -182,6 +182,71 @@ def test_linear_split_k(ops, M, N, K, S):
         L.tnt_debug_gemm_split_k(-1)
 
 
+def test_dropout_masks_match_host_generator(ops):
+    """tnt_dropout_apply against the numpy restatement of the counter-based generator: bit-exact mask, keep rate,
+    1/(1-p) scaling, residual add, distinct sites / seeds give distinct masks."""
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(300, 1024, generator=g) + 3.0
+    r = torch.randn(300, 1024, generator=g)
+    for p, seed, site in ((0.1, 7, 3), (0.5, 2 ** 63 + 11, 0xFFFF), (0.25, 0, 17)):
+        m = O.dropout_mask(p, seed, site, torch.arange(x.numel()).view(x.shape))
+        y = ops.dropout(x.cuda(), p, seed, site).cpu()
+        assert torch.equal(y, x * m)
+        assert abs((m == 0).float().mean().item() - p) < 5e-3
+        assert torch.equal(ops.dropout(x.cuda(), p, seed, site, residual=r.cuda()).cpu(), x * m + r)
+        yb = ops.dropout(x.bfloat16().cuda(), p, seed, site).cpu()
+        assert torch.equal(yb == 0, m == 0)
+    m1 = O.dropout_mask(0.1, 7, 3, torch.arange(100000))
+    assert (m1 != O.dropout_mask(0.1, 7, 4, torch.arange(100000))).float().mean() > 0.1
+    assert (m1 != O.dropout_mask(0.1, 8, 3, torch.arange(100000))).float().mean() > 0.1
+    assert torch.equal(ops.dropout(x.cuda(), 0.0, 1, 1).cpu(), x)
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_linear_epilogue_dropout(ops, dtype):
+    """dropout(a w^T + b) + residual and dropout(relu(.)) in the GEMM epilogues (tcgen05 persistent, split-K and SIMT)."""
+    from news_image_caption_b200 import _lib
+    g = torch.Generator().manual_seed(11)
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    for (M, N, K) in ((200, 1000, 256), (256, 1024, 4096)):
+        a = torch.randn(M, K, generator=g).to(dtype)
+        w = (torch.randn(N, K, generator=g) / K ** 0.5).to(dtype)
+        b = torch.randn(N, generator=g)
+        r = torch.randn(M, N, generator=g).to(dtype)
+        z = a.double() @ w.double().t() + b.double()
+        m = O.dropout_mask(0.2, 99, 5, torch.arange(M * N).view(M, N)).double()
+        y = ops.linear(a.cuda(), w.cuda(), b.cuda(), _lib.EPI_RESIDUAL, residual=r.cuda(), drop=(0.2, 99, 5))
+        assert rel_err(y, z * m + r.double()) < tol
+        y = ops.linear(a.cuda(), w.cuda(), b.cuda(), _lib.EPI_RELU, drop=(0.2, 99, 5))
+        assert rel_err(y, z.relu() * m) < tol
+        # explicit index layout: ld / group stride
+        y = ops.linear(a.cuda(), w.cuda(), b.cuda(), _lib.EPI_RESIDUAL, residual=r.cuda(), drop=(0.2, 99, 5, 3 * N, N))
+        m2g = O.dropout_mask(0.2, 99, 5, (torch.arange(M)[:, None] * (3 * N) + torch.arange(N)[None, :])).double()
+        assert rel_err(y, z * m2g + r.double()) < tol      # group 0 of a grouped call: offset 0
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize('T,B,H,K', [(32, 3, 4, 7), (45, 2, 16, 31), (5, 2, 2, 3)])
+def test_dynconv_tap_dropout(ops, dtype, T, B, H, K):
+    """weight_dropout (dynamic.py:305): forward and backward against autograd through the oracle with the same mask."""
+    g = torch.Generator().manual_seed(T + K)
+    Cc = H * 64
+    x = torch.randn(T, B, Cc, generator=g).to(dtype)
+    lg = torch.randn(T, B, H * K, generator=g).to(dtype)
+    dy = torch.randn(T, B, Cc, generator=g).to(dtype)
+    xr, lr = x.double().requires_grad_(True), lg.double().requires_grad_(True)
+    m = O.dropout_mask(0.3, 21, 1, torch.arange(T * B * H * K).view(T, B, H, K)).double()
+    wts = torch.softmax(lr.view(T, B, H, K), -1) * m
+    win = F.pad(xr, (0, 0, 0, 0, K - 1, 0)).unfold(0, K, 1)
+    y = torch.einsum('tbhrk,tbhk->tbhr', win.reshape(T, B, H, 64, K), wts).reshape(T, B, Cc)
+    gx, gl = torch.autograd.grad(y, [xr, lr], dy.double())
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    assert rel_err(ops.dynconv(x.cuda(), lg.cuda(), H, K, drop=(0.3, 21, 1)), y.detach()) < tol
+    dx, dl = ops.dynconv_bwd(x.cuda(), lg.cuda(), dy.cuda(), H, K, drop=(0.3, 21, 1))
+    assert rel_err(dx, gx) < tol
+    assert rel_err(dl, gl) < (1e-4 if dtype == torch.float32 else 3e-2)
+
+
 def test_wn_fold(ops):
     g = torch.Generator().manual_seed(2)
     v, gg = torch.randn(64, 40, generator=g), torch.randn(64, 1, generator=g)

@@ -65,6 +65,37 @@ def test_xattn_backward(ops, T, S, H, D, mode, dtype):
     assert rel_err(dq, gq) < tol and rel_err(dk, gk) < tol and rel_err(dv, gv) < tol
 
 
+@pytest.mark.parametrize('T,S,B,H,D', [(7, 20, 3, 4, 16), (32, 130, 3, 2, 64), (40, 514, 2, 4, 64), (64, 51, 2, 2, 64)])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_xattn_probability_dropout(ops, T, S, B, H, D, dtype):
+    """attention_dropout (multi_head.py:463): forward and backward of the SIMT (fp32, D != 64) and tcgen05 (bf16, D = 64)
+    kernels against fp64 autograd with the same counter-based mask; the soft-max normaliser stays un-dropped."""
+    g = torch.Generator().manual_seed(T * 100 + S)
+    E = H * D
+    q = torch.randn(T, B, E, generator=g).to(dtype)
+    k = torch.randn(S, B, E, generator=g).to(dtype)
+    v = torch.randn(S, B, E, generator=g).to(dtype)
+    do = torch.randn(T, B, E, generator=g).to(dtype)
+    scale = D ** -0.5
+    pad = torch.rand(B, S, generator=g) > 0.6
+    pad[:, -2:] = False
+    qd, kd, vd = [t.double().requires_grad_(True) for t in (q, k, v)]
+    s = torch.einsum('tbhd,sbhd->bhts', qd.view(T, B, H, D), kd.view(S, B, H, D)) * scale
+    s = s.masked_fill(pad[:, None, None, :], float('-inf'))
+    drop = (0.2, 4242, 6)
+    m = O.dropout_mask(*drop, torch.arange(B * H * T * S).view(B, H, T, S)).double()
+    o = torch.einsum('bhts,sbhd->tbhd', torch.softmax(s, -1) * m, vd.view(S, B, H, D)).reshape(T, B, E)
+    gq, gk, gv = torch.autograd.grad(o, [qd, kd, vd], do.double())
+    lse = torch.empty(B, H, T, dtype=torch.float32, device='cuda')
+    out, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, scale, pad_mask=pad.cuda(), mask_S=S - 2, lse=lse, drop=drop)
+    dq, dk, dv = ops.xattn_bwd(q.cuda(), k.cuda(), v.cuda(), out, do.cuda(), H, scale, pad_mask=pad.cuda(), mask_S=S - 2,
+                               lse=lse, drop=drop)
+    tol = 2e-5 if dtype == torch.float32 else 3e-2
+    assert rel_err(lse, torch.logsumexp(s.detach(), -1)) < (1e-4 if dtype == torch.float32 else 2e-2)
+    assert rel_err(out, o.detach()) < tol
+    assert rel_err(dq, gq) < tol and rel_err(dk, gk) < tol and rel_err(dv, gv) < tol
+
+
 @pytest.mark.parametrize('T,S,B,H', [(32, 514, 3, 4), (7, 130, 2, 2), (40, 51, 5, 16), (64, 1000, 2, 2)])
 def test_xattn_backward_tcgen05(ops, T, S, B, H):
     """The tcgen05 / TMEM backward kernel (bf16, D = 64, T <= 64, lse saved by the forward) against fp64
@@ -113,10 +144,10 @@ def make_decoder(cfg, sd, dtype):
     return dec
 
 
-def oracle_grads(f, scale):
+def oracle_grads(f, scale, drop=None):
     cfg = f['config']
     sd = O.leaf_state_dict(f['state_dict'], O.tied_output_keys(len(cfg['cutoffs'])))
-    X, _ = O.decoder_forward(f['prev'], f['contexts'], sd, cfg['heads'], cfg['cutoffs'], cfg['sources'])
+    X, _ = O.decoder_forward(f['prev'], f['contexts'], sd, cfg['heads'], cfg['cutoffs'], cfg['sources'], drop=drop)
     loss, n = O.adaptive_nll(X, f['target'], sd, cfg['cutoffs'])
     (loss * scale).backward()
     return loss.detach(), n, sd
@@ -148,6 +179,46 @@ def test_train_step_gradients(name, dtype):
         worst.append((err(p.grad, go), k))
     worst.sort(reverse=True)
     assert worst[0][0] < gtol, '\n'.join('%.3e %s' % w for w in worst[:12])
+
+
+DROP_CFG = dict(dropout=0.1, input_dropout=0.1, weight_dropout=0.1, attention_dropout=0.1, relu_dropout=0.05)
+
+
+@pytest.mark.parametrize('name', ['tell2_small.pt', 'tell4_small.pt'])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_train_step_gradients_with_dropout(name, dtype):
+    """Training mode (config.yaml:51-69 dropout rates; relu_dropout raised from 0 to exercise its site): loss and every
+    gradient against autograd through the oracle fed the SAME masks (the counter-based generator restated in numpy),
+    for two consecutive steps (step k draws its masks with seed + k)."""
+    f = torch.load(os.path.join(G, name), weights_only=False)
+    scale, seed = 0.37, 0x1234567890ABCDEF
+    dec = make_decoder(f['config'], f['state_dict'], dtype).enable_training()
+    dec.set_dropout(seed=seed, **DROP_CFG)
+    ctx = {k: v.cuda() for k, v in f['contexts'].items()}
+    loss_plain = oracle_grads(f, scale)[0]
+    for step in range(2):
+        loss_o, n_o, sd = oracle_grads(f, scale, O.DropoutMasks(seed=seed + step, **DROP_CFG))
+        assert abs(loss_o.item() - loss_plain.item()) > 1e-3 * abs(loss_plain.item())      # the masks do something
+        out = dec.train_step(f['prev'].cuda(), f['target'].cuda(), ctx, loss_scale=scale)
+        torch.cuda.synchronize()
+        tol = 1e-4 if dtype == torch.float32 else 2e-2
+        assert int(out[1].item()) == n_o
+        assert abs(out[0].item() - loss_o.item()) < tol * abs(loss_o.item()), (step, out[0].item(), loss_o.item())
+        # bf16: relative L2 per tensor as in test_train_step_gradients; the 1/(1-p) factors of 6 stacked dropout sites
+        # amplify the bf16 rounding of the stored activation gradients, hence 2e-1 (fp32 pins the math at 2e-4)
+        gtol = 2e-4 if dtype == torch.float32 else 2e-1
+        err = rel_err if dtype == torch.float32 else l2_err
+        worst = []
+        for k, p in dec.named_parameters():
+            if 'token_embedder_position' in k:
+                continue
+            worst.append((err(p.grad, sd[k].grad), k))
+        worst.sort(reverse=True)
+        assert worst[0][0] < gtol, 'step %d\n' % step + '\n'.join('%.3e %s' % w for w in worst[:12])
+    # switching dropout off again restores the parity configuration
+    dec.set_dropout()
+    out = dec.train_step(f['prev'].cuda(), f['target'].cuda(), ctx, loss_scale=scale)
+    assert abs(out[0].item() - loss_plain.item()) < (1e-4 if dtype == torch.float32 else 2e-2) * abs(loss_plain.item())
 
 
 def test_gradients_are_additive_over_batch_shards():
