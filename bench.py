@@ -157,9 +157,12 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--workload', default='fwd', choices=sorted(WORKLOADS),
                     help='fwd = BASELINE configs[1] (the default, driver-run line); train = configs[2]; fwd4 = configs[3]; gen = configs[4]')
+    ap.add_argument('--no-dropout', action='store_true', help='train workload: the p = 0 parity configuration instead of config.yaml dropout')
     args = ap.parse_args()
     global B_PER_GPU, SOURCES, WORKLOAD
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload])
+    if args.workload == 'train':
+        wl['what'] += ' (dropout p=0)' if args.no_dropout else ' (dropout 0.1 / input 0.1 / weight 0.1 / attention 0.1 as config.yaml)'
     B_PER_GPU, SOURCES = wl['B'], wl['sources']
     WORKLOAD = 'tell-decoder-%s L4 d1024 H16 K3/7/15/31 V50265 %s B%d/gpu T32 S%s' % (
         wl['tag'], wl['what'], B_PER_GPU, '49+512' if len(SOURCES) == 2 else '49+512+4+64')
@@ -202,6 +205,8 @@ def main():
     if args.workload == 'train':
         from news_image_caption_b200.trainer import Trainer
         trainer = Trainer(dec, t_total=100000)
+        if not args.no_dropout:     # the reference's training configuration (config.yaml:51-69), counter-based masks
+            dec.set_dropout(dropout=0.1, input_dropout=0.1, weight_dropout=0.1, attention_dropout=0.1, relu_dropout=0.0, seed=1234)
 
     gen = args.workload == 'gen'
     GEN_LEN = T

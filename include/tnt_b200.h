@@ -278,7 +278,8 @@ typedef struct {
   int kv_group;       /* beam search: query rows b*kv_group .. +kv_group-1 share the k / v / mask of batch entry b
                          (B counts query rows; 0 or 1 = one k / v entry per query row) */
   tnt_dropout drop;   /* dropout on the probabilities (multi_head.py:463), index ((b*H + h)*T + t)*(S + n_extra) + key;
-                         the soft-max normaliser (and `lse`) are those of the un-dropped probabilities */
+                         the soft-max normaliser (and `lse`) are those of the un-dropped probabilities; `weights`
+                         averages the dropped probabilities, as the reference does */
 } tnt_xattn_params;
 int tnt_xattn_fwd(const tnt_xattn_params* p, tnt_stream stream);
 

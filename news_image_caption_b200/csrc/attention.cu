@@ -204,7 +204,12 @@ __global__ void __launch_bounds__(kThreads) xattn_fwd_kernel(tnt_xattn_params p,
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const int key = key0 + lane + 32 * e;
-          if (key < S2) atomicAdd(w + key, __expf(s[qi][e] - ms) * inv);
+          if (key < S2) {
+            float pv = __expf(s[qi][e] - ms) * inv;
+            if (dr.thr)      // training: the reference averages the DROPPED probabilities (multi_head.py:463-482)
+              pv = drop_val(dr, ((static_cast<unsigned long long>(b) * p.H + h) * p.T + t0 + qw + qi) * S2 + key, pv);
+            atomicAdd(w + key, pv);
+          }
         }
       }
     }
@@ -236,7 +241,6 @@ int xattn_check(const tnt_xattn_params* p) {
   TNT_CHECK_ARG(p->B > 0 && p->T >= 0 && p->S >= 0 && p->H > 0, "xattn: bad shape");
   TNT_CHECK_ARG(p->D % 8 == 0 && p->D <= 128, "xattn: head dim %d must be a multiple of 8, <= 128", p->D);
   TNT_CHECK_ARG(p->drop.p >= 0.f && p->drop.p < 1.f, "xattn: dropout p = %f", p->drop.p);
-  TNT_CHECK_ARG(!(p->drop.p > 0.f) || !p->weights, "xattn: the head-averaged weights output is not available with dropout");
   TNT_CHECK_ARG(p->n_extra == 0 || p->n_extra == 2, "xattn: n_extra must be 0 or 2");
   TNT_CHECK_ARG(p->n_extra == 0 || (p->bias_k && p->bias_v), "xattn: bias_k / bias_v missing");
   TNT_CHECK_ARG(p->mask_mode == TNT_MASK_NONE || p->mask, "xattn: mask missing");

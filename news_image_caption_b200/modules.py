@@ -74,22 +74,27 @@ class GehringLinear(nn.Module):
         return linear(x, self.folded_weight(), self.bias)
 
 
+def _draw_seed():
+    """A 63-bit seed for one dropout call, drawn from torch's CPU generator (so torch.manual_seed controls it)."""
+    return int(torch.empty((), dtype=torch.int64).random_().item())
+
+
 class DynConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, logits, H, K, hist):
+    def forward(ctx, x, logits, H, K, hist, drop=None):
         x, logits = _c(x), _c(logits)
         ctx.save_for_backward(x, logits)
-        ctx.meta = (H, K, hist is not None)
-        return ops.dynconv(x, logits, H, K, hist=hist)
+        ctx.meta = (H, K, hist is not None, drop)
+        return ops.dynconv(x, logits, H, K, hist=hist, drop=drop)
 
     @staticmethod
     def backward(ctx, dy):
         x, logits = ctx.saved_tensors
-        H, K, had_hist = ctx.meta
+        H, K, had_hist, drop = ctx.meta
         if had_hist:
             raise RuntimeError('DynamicConv1dTBC: backward through the incremental path is not supported')
-        dx, dl = ops.dynconv_bwd(x, logits, _c(dy), H, K)
-        return dx, dl, None, None, None
+        dx, dl = ops.dynconv_bwd(x, logits, _c(dy), H, K, drop=drop)      # the mask is recomputed from (p, seed, site)
+        return dx, dl, None, None, None, None
 
 
 _INSTANCE_ID = [0]
@@ -120,8 +125,11 @@ class DynamicConv1dTBC(nn.Module):
     def forward(self, X, incremental_state=None, query=None, unfold=None):
         """X [T, B, C] -> [T, B, C].  `unfold` is accepted and ignored: the kernel is one algorithm for every T
         (the reference switches to the unfolded path only for T > 512, dynamic.py:102; same numbers)."""
-        if self.training and self.weight_dropout > 0:
-            raise NotImplementedError('DynamicConv1dTBC: weight_dropout is not implemented (use eval() or p = 0)')
+        drop = None
+        if self.training and self.weight_dropout > 0:       # dynamic.py:305: DropConnect on the soft-maxed taps
+            if incremental_state is not None:
+                raise NotImplementedError('DynamicConv1dTBC: weight_dropout on the incremental path')
+            drop = (self.weight_dropout, _draw_seed(), self._id)
         q = X if query is None else query
         logits = linear(q, self.weight_linear.weight, self.weight_linear.bias)
         hist = None
@@ -130,7 +138,7 @@ class DynamicConv1dTBC(nn.Module):
             window = X if hist is None else torch.cat([hist, X], 0)
             keep = self.kernel_size - 1
             incremental_state[self._key()] = window[-keep:].detach() if keep > 0 else window[:0]
-        return DynConvFn.apply(X, logits, self.num_heads, self.kernel_size, hist)
+        return DynConvFn.apply(X, logits, self.num_heads, self.kernel_size, hist, drop)
 
     def reorder_incremental_state(self, incremental_state, new_order):
         buf = incremental_state.get(self._key())
@@ -140,22 +148,22 @@ class DynamicConv1dTBC(nn.Module):
 
 class XattnFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, q, k, v, H, scale, pad_mask, mask_S, need_weights):
+    def forward(ctx, q, k, v, H, scale, pad_mask, mask_S, need_weights, drop=None):
         q, k, v = _c(q), _c(k), _c(v)
         T, B, E = q.shape
         lse = torch.empty(B, H, T, dtype=torch.float32, device=q.device)
-        out, w = ops.xattn(q, k, v, H, scale, pad_mask=pad_mask, mask_S=mask_S, need_weights=need_weights, lse=lse)
+        out, w = ops.xattn(q, k, v, H, scale, pad_mask=pad_mask, mask_S=mask_S, need_weights=need_weights, lse=lse, drop=drop)
         ctx.save_for_backward(q, k, v, out, lse)
-        ctx.meta = (H, scale, pad_mask, mask_S)
+        ctx.meta = (H, scale, pad_mask, mask_S, drop)
         ctx.mark_non_differentiable(w) if w is not None else None
         return out, w
 
     @staticmethod
     def backward(ctx, dout, _dw):
         q, k, v, out, lse = ctx.saved_tensors
-        H, scale, pad_mask, mask_S = ctx.meta
-        dq, dk, dv = ops.xattn_bwd(q, k, v, out, _c(dout), H, scale, pad_mask=pad_mask, mask_S=mask_S, lse=lse)
-        return dq, dk, dv, None, None, None, None, None
+        H, scale, pad_mask, mask_S, drop = ctx.meta
+        dq, dk, dv = ops.xattn_bwd(q, k, v, out, _c(dout), H, scale, pad_mask=pad_mask, mask_S=mask_S, lse=lse, drop=drop)
+        return dq, dk, dv, None, None, None, None, None, None
 
 
 class MultiHeadAttention(nn.Module):
@@ -203,8 +211,9 @@ class MultiHeadAttention(nn.Module):
         """query [T,B,E], key/value [S,B,kdim] -> (attn [T,B,E], head-averaged weights [B,T,S+2] | None)."""
         if attn_mask is not None:
             raise NotImplementedError('MultiHeadAttention: attn_mask is not used by the decoders and not implemented')
-        if self.training and self.dropout > 0:
-            raise NotImplementedError('MultiHeadAttention: attention dropout is not implemented (use eval() or p = 0)')
+        drop = None
+        if self.training and self.dropout > 0:              # multi_head.py:463: dropout on the probabilities
+            drop = (self.dropout, _draw_seed(), 0)      # the returned weights are the dropped ones, as in the reference
         T, B, E = query.shape
         S = key.shape[0]
         wq, wk, wv = self._weights()
@@ -216,7 +225,7 @@ class MultiHeadAttention(nn.Module):
         k = torch.cat([k, self.bias_k.to(k.dtype).expand(1, B, E), zeros], 0)      # :355-374, 416-421
         v = torch.cat([v, self.bias_v.to(v.dtype).expand(1, B, E), zeros], 0)
         out, w = XattnFn.apply(q, k, v, self.num_heads, self.scaling, key_padding_mask, S if key_padding_mask is not None else 0,
-                               need_weights)
+                               need_weights, drop)
         return linear(out, self.out_proj.weight, self.out_proj.bias), w
 
     def reorder_incremental_state(self, incremental_state, new_order):

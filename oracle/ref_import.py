@@ -121,7 +121,7 @@ def load_final_v2(variant='final_roberta2'):
 
 
 def build_ref_decoder(n_sources=2, d=1024, heads=16, ffn=4096, kernels=(3, 7, 15, 31),
-                      vocab=50265, cutoff=(5000, 20000), seed=0, article_dim=1024):
+                      vocab=50265, cutoff=(5000, 20000), seed=0, article_dim=1024, relu_dropout=0.0):
     """Reference decoder at the YAML hyper-parameters
     (ttl/expt/nytimes/9_transformer_objects/config.yaml:28-76), dropout irrelevant in eval()."""
     import torch
@@ -137,7 +137,7 @@ def build_ref_decoder(n_sources=2, d=1024, heads=16, ffn=4096, kernels=(3, 7, 15
                   share_decoder_input_output_embed=False, decoder_output_dim=d,
                   decoder_conv_dim=d, decoder_glu=True, decoder_conv_type='dynamic',
                   weight_softmax=True, decoder_attention_heads=heads, weight_dropout=0.1,
-                  relu_dropout=0.0, input_dropout=0.1, decoder_normalize_before=False,
+                  relu_dropout=relu_dropout, input_dropout=0.1, decoder_normalize_before=False,
                   attention_dropout=0.1, decoder_ffn_embed_dim=ffn,
                   decoder_kernel_size_list=list(kernels), adaptive_softmax_cutoff=list(cutoff),
                   tie_adaptive_weights=True, adaptive_softmax_dropout=0, tie_adaptive_proj=False,

@@ -43,3 +43,23 @@ def test_product_never_imports_oracle():
             if f.endswith(('.py', '.cu', '.cuh', '.h')):
                 src = open(os.path.join(dp, f)).read()
                 assert 'oracle' not in src.replace('the oracle', ''), os.path.join(dp, f)
+
+
+def test_dropout_generator_restatement(built):
+    """tnt_dropout_bits is a HOST function of the C ABI: the oracle's numpy restatement (oracle/restate.py dropout_bits)
+    must agree bit for bit -- it is what lets the training-step tests feed the kernels' masks to the oracle."""
+    import numpy as np
+    from news_image_caption_b200 import _lib
+    from oracle import restate as O
+    L = _lib.lib()
+    rng = np.random.default_rng(0)
+    idx = np.concatenate([np.arange(64, dtype=np.uint64), rng.integers(0, 2 ** 63, 200, dtype=np.uint64),
+                          np.array([2 ** 32 - 1, 2 ** 32, 2 ** 64 - 1], dtype=np.uint64)])
+    for seed, site in ((0, 0), (0x1234567890ABCDEF, 35), (2 ** 64 - 1, 0xFFFF), (42, 6 + 16 * 3)):
+        want = [L.tnt_dropout_bits(seed, site, int(i)) for i in idx]
+        assert O.dropout_bits(seed, site, idx).tolist() == want
+    bits = O.dropout_bits(7, 3, np.arange(1 << 20))
+    assert abs((bits < np.uint32(int(0.1 * 2 ** 32))).mean() - 0.1) < 2e-3          # keep rate
+    assert abs(np.corrcoef(bits[:-1].astype(np.float64), bits[1:].astype(np.float64))[0, 1]) < 5e-3   # neighbours uncorrelated
+    m = O.dropout_mask(0.1, 7, 3, __import__('torch').arange(1000))
+    assert set(m.unique().tolist()) <= {0.0, float(np.float32(1.0) / (np.float32(1.0) - np.float32(0.1)))}

@@ -76,6 +76,56 @@ def test_multi_head_attention_module(M, kdim):
         assert rel_err(p.grad, sd['a.' + k].grad) < 2e-4, k
 
 
+def _next_seed(s):
+    """The seed the module's next dropout call will draw after torch.manual_seed(s)."""
+    torch.manual_seed(s)
+    seed = int(torch.empty((), dtype=torch.int64).random_().item())
+    torch.manual_seed(s)
+    return seed
+
+
+def test_modules_in_training_mode_with_dropout(M):
+    """train(): DynamicConv1dTBC weight_dropout (dynamic.py:305) and MultiHeadAttention dropout (multi_head.py:463),
+    forward, returned (dropped) weights and autograd backward against the oracle fed the same counter-based masks."""
+    g = torch.Generator().manual_seed(4)
+    T, B, C, H, K = 11, 3, 64, 4, 7
+    m = M.DynamicConv1dTBC(C, K, padding_l=K - 1, num_heads=H, weight_softmax=True, weight_dropout=0.25).cuda().train()
+    x = torch.randn(T, B, C, generator=g)
+    gy = torch.randn(T, B, C, generator=g)
+    w = m.weight_linear.weight.detach().cpu().clone().requires_grad_(True)
+    xr = x.clone().requires_grad_(True)
+    seed = _next_seed(77)
+    yo = O.dynamic_conv(xr, w, H, K, lambda t: t * O.dropout_mask(0.25, seed, m._id, torch.arange(t.numel()).view(t.shape)))
+    yo.backward(gy)
+    xc = x.cuda().requires_grad_(True)
+    y = m(xc)
+    y.backward(gy.cuda())
+    assert rel_err(y, yo.detach()) < 1e-5
+    assert rel_err(xc.grad, xr.grad) < 1e-4 and rel_err(m.weight_linear.weight.grad, w.grad) < 1e-4
+    assert rel_err(m.eval()(x.cuda()), O.dynamic_conv(x, w.detach(), H, K)) < 1e-5        # eval(): identity
+
+    E, S = 64, 13
+    a = M.MultiHeadAttention(E, H, kdim=40, vdim=40, dropout=0.3).cuda().train()
+    sd = {'a.' + k: v.detach().cpu().clone().requires_grad_(True) for k, v in a.state_dict().items()}
+    q = torch.randn(T, B, E, generator=g)
+    mem = torch.randn(S, B, 40, generator=g)
+    pad = torch.rand(B, S, generator=g) > 0.6
+    qo = q.clone().requires_grad_(True)
+    seed = _next_seed(78)
+    kk, vv = O.mha_project_kv(mem, sd, 'a.', E)
+    out_o, w_o = O.mha_attend(qo, kk, vv, pad, sd, 'a.', H,
+                              lambda pr: pr * O.dropout_mask(0.3, seed, 0, torch.arange(pr.numel()).view(pr.shape)))
+    gy = torch.randn(T, B, E, generator=g)
+    out_o.backward(gy)
+    qc = q.cuda().requires_grad_(True)
+    out, wts = a(qc, mem.cuda(), mem.cuda(), key_padding_mask=pad.cuda(), static_kv=True)
+    out.backward(gy.cuda())
+    assert rel_err(out, out_o.detach()) < 1e-4 and rel_err(wts, w_o.detach()) < 1e-4
+    assert rel_err(qc.grad, qo.grad) < 1e-4
+    for k, p in a.named_parameters():
+        assert rel_err(p.grad, sd['a.' + k].grad) < 2e-4, k
+
+
 def test_gehring_linear_and_adaptive_softmax_modules(M):
     g = torch.Generator().manual_seed(3)
     lin = M.GehringLinear(48, 72).cuda()

@@ -81,6 +81,72 @@ def test_all_gradients_match_reference(nsrc, srcs):
         close(go, gr, 2e-4)
 
 
+@pytest.mark.parametrize('nsrc,srcs', [(2, ('image', 'article')), (4, ('image', 'article', 'faces', 'obj'))])
+def test_training_mode_dropout_sites_match_reference(monkeypatch, nsrc, srcs):
+    """Pins WHERE the oracle (and so the CUDA training step) applies dropout: the unmodified reference decoder in
+    train() mode with F.dropout patched to hand out the counter-based masks in the order the reference calls it
+    (decoder_flattened.py:109,283,289,308,326,340,342, dynamic.py:305, multi_head.py:463) -- forward, loss and every
+    gradient must equal the oracle's with DropoutMasks of the same seed."""
+    import torch.nn.functional as F
+    R = ri.load_tell()
+    d, H, kernels, V, cut = 32, 4, (3, 7), 300, (100, 200)
+    dec = ri.build_ref_decoder(nsrc, d=d, heads=H, ffn=48, kernels=kernels, vocab=V, cutoff=cut, seed=7, relu_dropout=0.05)
+    dec.train()
+    B, T = 3, 8
+    prev, tgt, ctx = synth.make_batch(B, T, V, srcs, seed=11, S_img=3, S_art=10, S_obj=4)
+    seed = 0xC0FFEE1234
+    cfg = dict(dropout=0.1, input_dropout=0.1, weight_dropout=0.1, attention_dropout=0.1, relu_dropout=0.05)
+    ns = len(srcs)
+    nat = lambda shape: torch.arange(int(torch.tensor(shape).prod())).view(*shape)
+    queue = [(cfg['dropout'], O.DROP_SITE_EMBED, lambda x: nat((T, B, d)).transpose(0, 1))]
+    for l in range(len(kernels)):
+        st = lambda kind, l=l: l * 16 + kind
+        queue.append((cfg['input_dropout'], st(O.DROP_INPUT), lambda x: nat(x.shape)))
+        queue.append((cfg['weight_dropout'], st(O.DROP_TAPS), lambda x: nat(x.shape)))
+        queue.append((cfg['dropout'], st(O.DROP_CONV_OUT), lambda x: nat(x.shape)))
+        for si in range(ns):
+            queue.append((cfg['attention_dropout'], st(O.DROP_ATTN_PROB + si), lambda x: nat(x.shape)))
+            queue.append((cfg['dropout'], st(O.DROP_ATTN_OUT),
+                          lambda x, si=si: (torch.arange(T * B)[:, None] * (ns * d) + si * d + torch.arange(d)[None, :]).view(T, B, d)))
+        queue.append((cfg['relu_dropout'], st(O.DROP_RELU), lambda x: nat(x.shape)))
+        queue.append((cfg['dropout'], st(O.DROP_FFN_OUT), lambda x: nat(x.shape)))
+    calls = []
+
+    def fake_dropout(x, p=0.5, training=True, inplace=False):
+        if not training or p == 0:
+            return x
+        want_p, site, index = queue[len(calls)]
+        assert abs(p - want_p) < 1e-12, (len(calls), p, want_p)
+        calls.append(site)
+        return x * O.dropout_mask(p, seed, site, index(x)).view(x.shape)
+
+    monkeypatch.setattr(F, 'dropout', fake_dropout)
+    X, _ = dec({'roberta': prev}, ctx)
+    loss, n = R.AdaptiveLoss(1)(dec.adaptive_softmax, (X, None), tgt)
+    assert len(calls) == len(queue)
+    params = dict(dec.named_parameters())
+    g_ref = dict(zip(params, torch.autograd.grad(loss, list(params.values()), allow_unused=True)))
+    monkeypatch.undo()
+    sd = O.leaf_state_dict(dec.state_dict(), O.tied_output_keys(len(cut) + 1))
+    Xo, _ = O.decoder_forward(prev, ctx, sd, H, list(cut) + [V], srcs, drop=O.DropoutMasks(seed=seed, **cfg))
+    close(Xo.detach(), X.detach())
+    lo, no = O.adaptive_nll(Xo, tgt, sd, list(cut) + [V])
+    assert n == no and abs(lo.item() - loss.item()) < 1e-4 * abs(loss.item())
+    lo.backward()
+    checked = 0
+    for k, gr in g_ref.items():
+        if gr is None or k not in sd or sd[k].grad is None:
+            continue
+        close(sd[k].grad, gr, 2e-4)
+        checked += 1
+    assert checked > 20 * len(kernels)
+    # and the masks matter: the eval-mode forward differs
+    dec.eval()
+    with torch.no_grad():
+        Xe, _ = dec({'roberta': prev}, ctx)
+    assert (Xe - X.detach()).abs().max() > 1e-2
+
+
 def test_v2_other_variant():
     torch.set_grad_enabled(False)
     tv = ri.load_final_v2('final_roberta2')
