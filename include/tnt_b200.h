@@ -394,6 +394,31 @@ size_t tnt_decoder_beam_workspace_bytes(const tnt_decoder* d, int B, int beam, i
 int tnt_decoder_generate_beam(tnt_decoder* d, const int64_t* seed, const tnt_contexts* ctx, int gen_len, int eos, int beam,
                               int64_t* seq_out, float* logp_out, float* p_out, void* workspace, size_t workspace_bytes,
                               tnt_stream stream);
+/* embedder output (adaptive band embedding * sqrt(d) + sinusoidal position, decoder_flattened.py:96-99) for ids [B, T]:
+ * out [T*B, d] engine dtype, row t*B + b (the layout the layers run on).  The pointer decoder's `inp_embed`. */
+int tnt_decoder_embed(tnt_decoder* d, const int64_t* ids, int B, int T, void* out_tb, tnt_stream stream);
+
+/* Copy head of DynamicConvDecoderPointer (decoder_pointer.py:138-141, 151-216), in place on the
+ * full-vocabulary log-probabilities of tnt_decoder_log_prob:
+ *   p_gen  = sigmoid(w_pgen[:d] . inp_embed + w_pgen[d:] . x + b_pgen)          project_p_gens(cat(inp_embed, X))
+ *   probs  = p_gen * exp(logprob) + scatter_add(article_ids, (1 - p_gen) * attn[:, :, :S])
+ *   logprob <- log(clamp(probs, 1e-10, 1)) */
+typedef struct {
+  const void* x; int64_t ldx;              /* decoder output [B*T, d] engine dtype, row b*T + t */
+  const void* inp_embed; int64_t lde;      /* embedder output [T*B, d], row t*B + b (tnt_decoder_embed) */
+  const float* w_pgen; float b_pgen;       /* weight-norm-folded project_p_gens weight [2d] and bias */
+  const float* attn; int64_t attn_ld;      /* [B*T, attn_ld >= S] head-averaged article attention of the last layer
+                                              (tnt_decoder_forward attn_out: the 2 extra keys are simply not read) */
+  const int64_t* article_ids;              /* [B, S] token ids of the article positions */
+  float* logprob; int64_t ldp;             /* [B*T, V] fp32, in / out */
+  float* p_gen;                            /* optional [B*T] */
+  int B, T, S, d, V, dtype;
+} tnt_pointer_params;
+int tnt_pointer_mix(const tnt_pointer_params* p, tnt_stream stream);
+/* F.nll_loss(logprob, target, ignore_index = pad, reduction = 'sum') (transformer_context_pointer.py:128):
+ * out2 = [sum, number of counted rows] */
+int tnt_nll_rows(const float* logprob, int64_t ldp, const int64_t* target, int rows, int pad, float* out2, tnt_stream stream);
+
 size_t tnt_decoder_generate_workspace_bytes(const tnt_decoder* d, int B, int gen_len, const int* S);
 int tnt_decoder_generate(tnt_decoder* d, const int64_t* seed, const tnt_contexts* ctx, int gen_len, int eos,
                          int64_t* ids_out, float* logp_out, int* steps_host, void* workspace,

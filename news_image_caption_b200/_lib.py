@@ -38,6 +38,12 @@ def drop_site(layer, kind):
     return layer * 16 + kind
 
 
+class PointerParams(C.Structure):
+    _fields_ = [('x', vp), ('ldx', i64), ('inp_embed', vp), ('lde', i64), ('w_pgen', vp), ('b_pgen', f32), ('attn', vp),
+                ('attn_ld', i64), ('article_ids', vp), ('logprob', vp), ('ldp', i64), ('p_gen', vp), ('B', i32), ('T', i32),
+                ('S', i32), ('d', i32), ('V', i32), ('dtype', i32)]
+
+
 class LinearParams(C.Structure):
     _fields_ = [('a', vp), ('lda', i64), ('w', vp), ('ldw', i64), ('bias', vp), ('residual', vp), ('ldr', i64),
                 ('c', vp), ('ldc', i64), ('M', i32), ('N', i32), ('K', i32), ('m_dyn', vp), ('groups', i32),
@@ -163,6 +169,9 @@ _SIGS = {
     'tnt_decoder_forward': (i32, [vp, vp, C.POINTER(Contexts), vp, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_nll': (i32, [vp, vp, vp, i32, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_log_prob': (i32, [vp, vp, i32, vp, vp, C.c_size_t, vp]),
+    'tnt_decoder_embed': (i32, [vp, vp, i32, i32, vp, vp]),
+    'tnt_pointer_mix': (i32, [C.POINTER(PointerParams), vp]),
+    'tnt_nll_rows': (i32, [vp, i64, vp, i32, i32, vp, vp]),
     'tnt_decoder_generate_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
     'tnt_decoder_generate': (i32, [vp, vp, C.POINTER(Contexts), i32, i32, vp, vp, C.POINTER(i32), vp, C.c_size_t, vp]),
     'tnt_decoder_beam_workspace_bytes': (C.c_size_t, [vp, i32, i32, i32, C.POINTER(i32)]),

@@ -251,6 +251,12 @@ extern "C" int tnt_decoder_forward(tnt_decoder* D, const int64_t* ids, const tnt
   return TNT_OK;
 }
 
+extern "C" int tnt_decoder_embed(tnt_decoder* D, const int64_t* ids, int B, int T, void* out_tb, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized && ids && out_tb && B > 0 && T > 0, "decoder_embed: bad arguments");
+  TNT_CHECK_ARG(T + D->cfg.pad_idx + 1 <= D->cfg.max_positions, "decoder_embed: T=%d exceeds the position table", T);
+  return embed(D, ids, B, T, out_tb, nullptr, as_stream(stream));
+}
+
 extern "C" int tnt_decoder_nll(tnt_decoder* D, const void* X, const int64_t* target, int n_rows, float* out2,
                                void* workspace, size_t workspace_bytes, tnt_stream stream) {
   TNT_CHECK_ARG(D && D->finalized && X && target && out2 && workspace, "decoder_nll: bad arguments");

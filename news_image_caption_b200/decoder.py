@@ -98,6 +98,7 @@ class DynamicConvDecoder(nn.Module):
     """B200 engine behind the reference `DynamicConvDecoder` / `DynamicConvFacesObjectsDecoder` API
     (post-LN, GLU, dynamic conv, weight_softmax, adaptive softmax with tied weights: the configuration
     every shipped experiment uses, ttl/expt/*/config.yaml)."""
+    HOST_SIDE_KEYS = ('\0',)          # prefixes of parameters that are not fed to the engine handle (none here)
 
     def __init__(self, decoder_output_dim=1024, decoder_attention_heads=16, decoder_ffn_embed_dim=4096,
                  decoder_kernel_size_list=(3, 7, 15, 31), vocab_size=50265, adaptive_softmax_cutoff=(5000, 20000),
@@ -171,6 +172,8 @@ class DynamicConvDecoder(nn.Module):
             _lib.check(L.tnt_decoder_bind_weights(self._handle, _ptr(self._weights), nbytes), 'bind_weights')
         keep = []
         for k, p in self.named_parameters(remove_duplicate=False):
+            if k.startswith(self.HOST_SIDE_KEYS):       # parameters of heads that live outside the engine handle
+                continue
             t = p.detach().contiguous()
             keep.append(t)
             shp = (C.c_int64 * t.dim())(*t.shape)
@@ -465,6 +468,65 @@ class DynamicConvDecoder(nn.Module):
     def score_host_wait(self, slot):
         _lib.check(_lib.lib().tnt_decoder_score_host_wait(self._h(), slot), 'tnt_decoder_score_host_wait')
         return float(self._out2s[slot][0]), float(self._out2s[slot][1])
+
+
+class DynamicConvDecoderPointer(DynamicConvDecoder):
+    """`DynamicConvDecoderPointer` (ttl/tell/models/decoder_pointer.py:23-297; expt/goodnews/h3_context_pointer): the
+    2-source decoder plus a copy head -- p_gen = sigmoid(project_p_gens(cat(inp_embed, X))) mixes the vocabulary
+    distribution with the last layer's article attention scattered onto the article's token ids.  Inference / scoring
+    path; forward(prev_target, contexts, article_ids) -> (lprobs [B, T, V], {'attn', 'p_gens'})."""
+    HOST_SIDE_KEYS = ('project_p_gens.',)
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        dev = next(self.parameters()).device
+        _register(self, 'project_p_gens.bias', torch.zeros(1, device=dev))
+        _register(self, 'project_p_gens.weight_g', torch.ones(1, 1, device=dev))
+        _register(self, 'project_p_gens.weight_v', torch.zeros(1, 2 * self.d, device=dev))
+
+    def forward(self, prev_target, contexts, article_ids, incremental_state=None, need_attn=True):
+        from . import ops
+        X, extra = super().forward(prev_target, contexts, incremental_state, need_attn=True)
+        ids = prev_target['roberta'] if isinstance(prev_target, dict) else prev_target
+        ids = ids.to('cuda', torch.long).contiguous()
+        B, T = ids.shape
+        L, h = _lib.lib(), self._h()
+        emb = torch.empty(T * B, self.d, dtype=self.torch_dtype, device='cuda')
+        _lib.check(L.tnt_decoder_embed(h, _ptr(ids), B, T, _ptr(emb), _stream()), 'tnt_decoder_embed')
+        lp = self.get_normalized_probs((X, None), log_probs=True)                 # [B, T, V] fp32
+        pg = self.project_p_gens
+        w = ops.wn_fold(pg.weight_v.detach(), pg.weight_g.detach()).view(-1).contiguous()     # g * v / ||v||, fp32 [2d]
+        art = article_ids.to('cuda', torch.long).contiguous()
+        attn = extra['attn']
+        p = _lib.PointerParams()
+        p.x, p.ldx, p.inp_embed, p.lde = X.data_ptr(), self.d, emb.data_ptr(), self.d
+        p.w_pgen, p.b_pgen = w.data_ptr(), float(pg.bias.item())
+        p.attn, p.attn_ld, p.article_ids = attn.data_ptr(), attn.shape[2], art.data_ptr()
+        p_gen = torch.empty(B, T, 1, dtype=torch.float32, device='cuda')
+        p.logprob, p.ldp, p.p_gen = lp.data_ptr(), self.vocab, p_gen.data_ptr()
+        p.B, p.T, p.S, p.d, p.V, p.dtype = B, T, art.shape[1], self.d, self.vocab, self.dtype_code
+        if art.shape != (B, attn.shape[2] - 2):
+            raise ValueError('article_ids must be [B, S_article]')
+        _lib.check(L.tnt_pointer_mix(C.byref(p), _stream()), 'tnt_pointer_mix')
+        return lp, {'attn': attn, 'p_gens': p_gen, 'inner_states': None}
+
+    def nll(self, lprobs, target):
+        """F.nll_loss(lprobs, target, ignore_index=pad, reduction='sum') (transformer_context_pointer.py:128):
+        device tensor [loss_sum, n_non_pad]."""
+        lp = lprobs.contiguous().view(-1, lprobs.shape[-1])
+        tg = target.to('cuda', torch.long).contiguous().view(-1)
+        out = torch.empty(2, dtype=torch.float32, device='cuda')
+        _lib.check(_lib.lib().tnt_nll_rows(_ptr(lp), lp.shape[1], _ptr(tg), lp.shape[0], self.pad, _ptr(out), _stream()),
+                   'tnt_nll_rows')
+        return out
+
+    def train_step(self, *a, **k):
+        raise NotImplementedError('DynamicConvDecoderPointer: the copy head is implemented for inference / scoring only')
+
+    def generate(self, *a, **k):
+        raise NotImplementedError('DynamicConvDecoderPointer: generation through the copy head is not implemented')
+
+    generate_beam = generate
 
 
 class AdaptiveLoss(nn.Module):

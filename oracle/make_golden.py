@@ -157,6 +157,28 @@ def v2_case():
     print('v2_small.pt loss', float(loss))
 
 
+def pointer_case():
+    """Row f4: the unmodified DynamicConvDecoderPointer (decoder_pointer.py): lprobs of the copy head + the model's loss."""
+    import torch.nn.functional as F
+    ri.load_tell()
+    d, H, V, cut = 32, 4, 300, (100, 200)
+    dec = ri.build_ref_decoder('pointer', d=d, heads=H, ffn=64, kernels=(3, 7), vocab=V, cutoff=cut, seed=17)
+    torch.manual_seed(2)
+    dec.project_p_gens.weight_v.normal_(0, 0.4)
+    dec.project_p_gens.bias.fill_(-0.3)
+    prev, tgt, ctx = synth.make_batch(4, 10, V, ('image', 'article'), S_img=5, S_art=12)
+    art_ids = torch.randint(0, V, (4, 12), generator=torch.Generator().manual_seed(5))
+    art_ids[:, 7] = art_ids[:, 1]
+    lp, ex = dec({'roberta': prev}, ctx, art_ids)
+    loss = F.nll_loss(lp.view(-1, V), tgt.view(-1), ignore_index=1, reduction='sum')
+    fix = dict(config=dict(n_sources=2, sources=['image', 'article'], d=d, heads=H, ffn=64, kernels=[3, 7], vocab=V,
+                           cutoffs=list(cut) + [V]),
+               state_dict={k: v.clone() for k, v in dec.state_dict().items()}, prev=prev, target=tgt, contexts=ctx,
+               article_ids=art_ids, lprobs=lp, attn=ex['attn'], loss=loss, ntokens=int((tgt != 1).sum()))
+    torch.save(fix, os.path.join(OUT, 'pointer_small.pt'))
+    print('pointer_small.pt loss', float(loss), os.path.getsize(os.path.join(OUT, 'pointer_small.pt')) // 1024, 'KiB')
+
+
 def main():
     warnings.filterwarnings('ignore')
     os.makedirs(OUT, exist_ok=True)
@@ -168,6 +190,7 @@ def main():
     dynconv_cases()
     mha_cases()
     v2_case()
+    pointer_case()
 
 
 if __name__ == '__main__':

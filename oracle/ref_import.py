@@ -90,7 +90,9 @@ def load_tell():
                                               SumTextFieldEmbedder)
     dec2 = importlib.import_module('tell.models.decoder_flattened')
     dec4 = importlib.import_module('tell.models.decoder_faces_objects')
+    decp = importlib.import_module('tell.models.decoder_pointer')
     ns = types.SimpleNamespace(
+        DynamicConvDecoderPointer=decp.DynamicConvDecoderPointer,
         DynamicConv1dTBC=M.DynamicConv1dTBC, MultiHeadAttention=M.MultiHeadAttention,
         AdaptiveSoftmax=M.AdaptiveSoftmax, GehringLinear=M.GehringLinear,
         AdaptiveLoss=AdaptiveLoss, AdaptiveEmbedding=AdaptiveEmbedding,
@@ -147,6 +149,8 @@ def build_ref_decoder(n_sources=2, d=1024, heads=16, ffn=4096, kernels=(3, 7, 15
         dec = R.DynamicConvDecoder(article_embed_size=article_dim, **common)
     elif n_sources == 4:
         dec = R.DynamicConvFacesObjectsDecoder(**common)
+    elif n_sources == 'pointer':      # 2 sources + copy head (decoder_pointer.py)
+        dec = R.DynamicConvDecoderPointer(article_embed_size=article_dim, **common)
     else:
         raise ValueError(n_sources)
     dec.eval()

@@ -393,6 +393,29 @@ def decoder_forward(ids: torch.Tensor, contexts: dict, sd: SD, H: int, cutoffs: 
     return X.transpose(0, 1), attn
 
 
+def pointer_output_layer(X: torch.Tensor, inp_embed: torch.Tensor, attn: torch.Tensor, article_ids: torch.Tensor,
+                         sd: SD, cutoffs: Sequence[int]):
+    """Copy head of DynamicConvDecoderPointer -- decoder_pointer.py:138-141 (p_gens = project_p_gens(cat(inp_embed, X)))
+    and :151-216 (output_layer): probs = sigmoid(p_gens) * softmax_vocab(X) + scatter_add over the article token ids of
+    (1 - sigmoid(p_gens)) * attn[:, :, :-2]; lprobs = log(clamp(probs, 1e-10, 1)).  X, inp_embed [B,T,d]; attn [B,T,S+2]
+    (head-averaged article attention of the last layer); article_ids [B,S].  Returns (lprobs [B,T,V], p_gen [B,T,1])."""
+    p_gens = torch.sigmoid(gehring_linear(torch.cat((inp_embed, X), 2), sd, 'project_p_gens.'))
+    gen = adaptive_log_prob(X, sd, cutoffs).exp() * p_gens
+    B, T, V = gen.shape
+    copy = attn[:, :, :-2].float() * (1 - p_gens)
+    index = article_ids[:, None, :].expand(B, T, article_ids.shape[1])
+    dist = torch.zeros(B, T, V).scatter_add_(2, index.long(), copy)
+    return (gen + dist).clamp(1e-10, 1.0).log(), p_gens
+
+
+def pointer_decoder_forward(ids: torch.Tensor, contexts: dict, article_ids: torch.Tensor, sd: SD, H: int,
+                            cutoffs: Sequence[int]):
+    """DynamicConvDecoderPointer.forward (decoder_pointer.py:98-149), eval mode: lprobs [B,T,V], attn, p_gen."""
+    X, attn = decoder_forward(ids, contexts, sd, H, cutoffs, ('image', 'article'))
+    lp, pg = pointer_output_layer(X, embed(ids, sd, cutoffs), attn, article_ids, sd, cutoffs)
+    return lp, attn, pg
+
+
 def greedy_generate(seed_ids: torch.Tensor, contexts: dict, sd: SD, H: int,
                     cutoffs: Sequence[int], sources=('image', 'article'), gen_len: int = 100,
                     eos: int = 2, pad: int = 1):

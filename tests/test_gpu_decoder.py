@@ -64,6 +64,68 @@ def test_golden_greedy_fp32_bit_exact(name):
     assert rel_err(lp, f['greedy_logprobs']) < 1e-4
 
 
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_pointer_decoder_golden(dtype):
+    """Row f4 (decoder_pointer.py): lprobs of the copy head, the returned attention and the model's nll_loss against the
+    fixture frozen from the unmodified reference, and at full vocabulary width against the oracle."""
+    from news_image_caption_b200 import DynamicConvDecoderPointer, build
+    build.build()
+    f = torch.load(os.path.join(G, 'pointer_small.pt'), weights_only=False)
+    cfg = f['config']
+    dec = DynamicConvDecoderPointer(decoder_output_dim=cfg['d'], decoder_attention_heads=cfg['heads'],
+                                    decoder_ffn_embed_dim=cfg['ffn'], decoder_kernel_size_list=cfg['kernels'],
+                                    vocab_size=cfg['vocab'], adaptive_softmax_cutoff=cfg['cutoffs'][:-1],
+                                    sources=cfg['sources'], dtype=dtype)
+    dec.load_reference_state_dict(f['state_dict'])
+    lp, ex = dec({'roberta': f['prev'].cuda()}, cuda_ctx(f['contexts']), f['article_ids'].cuda())
+    tol = 1e-4 if dtype == torch.float32 else 2e-2
+    assert lp.shape == f['lprobs'].shape
+    # compare probabilities where they matter and log-probs everywhere they are not clamped noise
+    assert rel_err(lp.exp(), f['lprobs'].exp()) < tol
+    big = f['lprobs'] > -12
+    assert (lp.cpu()[big] - f['lprobs'][big]).abs().max().item() < (1e-3 if dtype == torch.float32 else 1e-1)
+    assert rel_err(ex['attn'], f['attn']) < tol
+    out = dec.nll(lp, f['target'].cuda())
+    assert int(out[1].item()) == f['ntokens']
+    assert abs(out[0].item() - f['loss'].item()) < tol * abs(f['loss'].item())
+    with pytest.raises(NotImplementedError):
+        dec.generate(f['prev'][:, :1].cuda(), cuda_ctx(f['contexts']))
+
+
+def test_pointer_mix_full_vocab():
+    """The copy-head kernel at V = 50265 (row resident in shared memory), d = 1024, bf16 inputs, against the oracle's
+    output_layer arithmetic on the same log-probs / attention; repeated and out-of-range-free article ids."""
+    import ctypes as C
+    from news_image_caption_b200 import _lib, build
+    build.build()
+    _lib.require_device()
+    g = torch.Generator().manual_seed(9)
+    B, T, S, d, V = 3, 5, 512, 1024, 50265
+    X = torch.randn(B, T, d, generator=g).bfloat16()
+    E = torch.randn(T, B, d, generator=g).bfloat16()
+    w = torch.randn(2 * d, generator=g) * 0.02
+    lp0 = torch.log_softmax(torch.randn(B, T, V, generator=g) * 3, -1)
+    attn = torch.softmax(torch.randn(B, T, S + 2, generator=g) * 2, -1)
+    ids = torch.randint(0, V, (B, S), generator=g)
+    ids[:, 100:200] = ids[:, :100]
+    pg = torch.sigmoid(torch.cat((E.transpose(0, 1).float(), X.float()), 2) @ w + 0.1)[..., None]
+    want = lp0.exp() * pg
+    want.scatter_add_(2, ids[:, None, :].expand(B, T, S), attn[:, :, :-2] * (1 - pg))
+    want = want.clamp(1e-10, 1.0).log()
+    Xc, Ec, wc, lpc, ac, ic = X.cuda(), E.cuda(), w.cuda(), lp0.clone().cuda(), attn.cuda(), ids.cuda()
+    pgc = torch.empty(B, T, device='cuda')
+    p = _lib.PointerParams()
+    p.x, p.ldx, p.inp_embed, p.lde, p.w_pgen, p.b_pgen = Xc.data_ptr(), d, Ec.data_ptr(), d, wc.data_ptr(), 0.1
+    p.attn, p.attn_ld, p.article_ids, p.logprob, p.ldp, p.p_gen = ac.data_ptr(), S + 2, ic.data_ptr(), lpc.data_ptr(), V, pgc.data_ptr()
+    p.B, p.T, p.S, p.d, p.V, p.dtype = B, T, S, d, V, _lib.TNT_BF16
+    _lib.check(_lib.lib().tnt_pointer_mix(C.byref(p), None), 'tnt_pointer_mix')
+    torch.cuda.synchronize()
+    assert rel_err(pgc, pg[..., 0]) < 1e-4
+    assert rel_err(lpc.exp(), want.exp()) < 1e-4
+    # total mass = 1 - (1 - p_gen) * (attention mass on the two extra keys the reference drops, decoder_pointer.py:191)
+    assert (lpc.exp().sum(-1).cpu() - want.exp().sum(-1)).abs().max() < 1e-4
+
+
 def test_generate_matches_teacher_forcing_bf16():
     """size-independent property: feeding the greedy ids back through the teacher-forced forward
     reproduces (argmax of) the same tokens -- incremental state == full-sequence path."""

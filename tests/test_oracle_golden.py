@@ -86,3 +86,17 @@ def test_v2():
     assert abs(loss.item() - f['loss'].item()) <= 1e-4 * abs(f['loss'].item())
     ys = O.v2_translate(f['memory'], sd, h, f['greedy'].shape[1])
     assert torch.equal(ys, f['greedy'])
+
+
+def test_pointer_decoder():
+    """Row f4: the oracle's copy head against the fixture frozen from the unmodified DynamicConvDecoderPointer."""
+    f = load('pointer_small.pt')
+    cfg = f['config']
+    lp, attn, pg = O.pointer_decoder_forward(f['prev'], f['contexts'], f['article_ids'], f['state_dict'], cfg['heads'],
+                                             cfg['cutoffs'])
+    close(lp, f['lprobs'])
+    close(attn, f['attn'])
+    tgt = f['target'].view(-1)
+    m = tgt != 1
+    loss = -lp.view(-1, cfg['vocab'])[m, tgt[m]].sum()
+    assert int(m.sum()) == f['ntokens'] and abs(loss.item() - f['loss'].item()) < 1e-4 * abs(f['loss'].item())

@@ -147,6 +147,32 @@ def test_training_mode_dropout_sites_match_reference(monkeypatch, nsrc, srcs):
     assert (Xe - X.detach()).abs().max() > 1e-2
 
 
+def test_pointer_decoder_matches_reference():
+    """Row f4: the copy head of the unmodified DynamicConvDecoderPointer (decoder_pointer.py) against the oracle's
+    pointer_decoder_forward, incl. repeated article token ids (scatter_add) and the nll_loss the model applies."""
+    import torch.nn.functional as F
+    torch.set_grad_enabled(False)
+    ri.load_tell()
+    d, H, V, cut = 64, 8, 500, (120, 300)
+    dec = ri.build_ref_decoder('pointer', d=d, heads=H, ffn=96, kernels=(3, 15), vocab=V, cutoff=cut, seed=13)
+    torch.manual_seed(1)
+    dec.project_p_gens.weight_v.normal_(0, 0.3)
+    dec.project_p_gens.bias.fill_(0.2)
+    sd = dec.state_dict()
+    prev, tgt, ctx = synth.make_batch(4, 9, V, ('image', 'article'), seed=21, S_img=4, S_art=17)
+    art_ids = torch.randint(0, V, (4, 17), generator=torch.Generator().manual_seed(3))
+    art_ids[:, 5] = art_ids[:, 2]                              # a token that occurs twice in the article
+    lp, ex = dec({'roberta': prev}, ctx, art_ids)
+    lo, attn, pg = O.pointer_decoder_forward(prev, ctx, art_ids, sd, H, list(cut) + [V])
+    close(lo, lp)
+    close(attn, ex['attn'])
+    assert (pg > 0.05).all() and (pg < 0.95).all()            # the mix is exercised on both sides
+    loss = F.nll_loss(lp.view(-1, V), tgt.view(-1), ignore_index=1, reduction='sum')
+    mask = tgt.view(-1) != 1
+    assert abs((-lo.view(-1, V)[mask, tgt.view(-1)[mask]].sum() - loss).item()) < 1e-4 * abs(loss.item())
+    torch.set_grad_enabled(True)
+
+
 def test_v2_other_variant():
     torch.set_grad_enabled(False)
     tv = ri.load_final_v2('final_roberta2')
