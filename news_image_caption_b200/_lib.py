@@ -101,7 +101,7 @@ class XattnParams(C.Structure):
                 ('o_stride_t', i64), ('o_stride_b', i64), ('mask', vp), ('m_stride_b', i64), ('m_stride_t', i64),
                 ('bias_k', vp), ('bias_v', vp), ('weights', vp), ('B', i32), ('T', i32), ('S', i32), ('H', i32),
                 ('D', i32), ('n_extra', i32), ('mask_mode', i32), ('scale', f32), ('dtype', i32), ('mask_S', i32), ('lse', vp), ('kv_group', i32),
-                ('drop', Dropout)]
+                ('drop', Dropout), ('tile_live', vp)]
 
 
 class XattnBwdParams(C.Structure):
@@ -154,6 +154,7 @@ _SIGS = {
     'tnt_context_mix': (i32, [C.POINTER(ContextMixParams), vp]),
     'tnt_nan_mask': (i32, [C.POINTER(NanMaskParams), vp]),
     'tnt_xattn_fwd': (i32, [C.POINTER(XattnParams), vp]),
+    'tnt_xattn_tile_mask': (i32, [vp, i64, i32, i32, i32, vp, vp]),
     'tnt_xattn_bwd_scratch_bytes': (C.c_size_t, [i32, i32, i32, i32]),
     'tnt_xattn_bwd': (i32, [C.POINTER(XattnBwdParams), vp]),
     'tnt_lse_workspace_bytes': (C.c_size_t, [i32, i32, i32]),

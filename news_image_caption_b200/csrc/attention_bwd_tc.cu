@@ -33,7 +33,8 @@ constexpr int KV_STAGE = 2 * KV_HALF;             // K | V
 constexpr int KVS = 2;
 constexpr int P_BYTES = TKEYS * 128;              // [128 keys x 64 (h,q)] bf16
 constexpr uint32_t COL_S = 0, COL_DP = 64, COL_DV = 128, COL_DK = 256, COL_DQ = 384;
-constexpr int SMEM_BYTES = 2 * MAXQT * QT_BYTES + KVS * KV_STAGE + 2 * P_BYTES + 2048 + 1024 + 1024;
+constexpr int kListBytes = 2048 * 4 + 128;
+constexpr int SMEM_BYTES = 2 * MAXQT * QT_BYTES + KVS * KV_STAGE + 2 * P_BYTES + 2048 + 1024 + 1024 + kListBytes;
 
 struct Args {
   const uint8_t* mask; long m_stride_b;
@@ -44,7 +45,40 @@ struct Args {
   float scale, scale_log2e;
   int n_items, n_qt, n_tiles;
   DropSpec drop;                                  // the forward's dropout on the probabilities
+  const uint32_t* tile_live;                      // optional [B]: bit i set = key tile i of batch row b holds an un-masked key
 };
+
+// sorted work list in shared memory (see attention_tc.cu): entry = batch row | (key tiles to visit) << 16; skipped tiles
+// get zero dK / dV rows without being loaded
+constexpr int kMaxList = 2048;
+__device__ __forceinline__ void build_work_list(const uint32_t* tile_live, int B, int n_tiles, uint32_t* wl, int* hist, int lane) {
+  const uint32_t all = (1u << n_tiles) - 1u;
+  if (lane < 18) hist[lane] = 0;
+  __syncwarp();
+  for (int b = lane; b < B; b += 32) {
+    uint32_t m = tile_live[b] & all;
+    if (!m) m = 1u;
+    atomicAdd(&hist[__popc(m)], 1);
+  }
+  __syncwarp();
+  if (lane == 0) {
+    int o = 0;
+    for (int c = 17; c >= 0; --c) {
+      const int n = hist[c];
+      hist[c] = o;
+      o += n;
+    }
+  }
+  __syncwarp();
+  for (int b = lane; b < B; b += 32) {
+    uint32_t m = tile_live[b] & all;
+    if (!m) m = 1u;
+    wl[atomicAdd(&hist[__popc(m)], 1)] = static_cast<uint32_t>(b) | (m << 16);
+  }
+}
+__device__ __forceinline__ uint32_t slot_entry(const uint32_t* wl, bool listed, int bi, int n_tiles) {
+  return listed ? wl[bi] : (static_cast<uint32_t>(bi) | (((1u << n_tiles) - 1u) << 16));
+}
 
 struct Bars {
   uint64_t q_full, q_empty, s_ready, s_empty, p_ready, p_empty, acc_ready, acc_empty, dq_ready, dq_empty;
@@ -52,6 +86,7 @@ struct Bars {
   uint32_t tmem;
 };
 
+template <bool DROP>
 __global__ void __launch_bounds__(kThreads, 1)
 xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmDO,
                     const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, Args a) {
@@ -64,9 +99,12 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint8_t* sDS = sP + P_BYTES;
   float* sStat = reinterpret_cast<float*>(sDS + P_BYTES);   // [2: lse2 | delta][2 heads][MAXQT*32]
   Bars* bar = reinterpret_cast<Bars*>(reinterpret_cast<uint8_t*>(sStat) + 2048);
+  uint32_t* wl = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(bar) + 1024);
+  int* wl_hist = reinterpret_cast<int*>(wl + kMaxList);
+  const bool listed = a.tile_live != nullptr && a.B <= kMaxList;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_tiles = a.n_tiles, n_qt = a.n_qt, n_iter = n_tiles * n_qt;
+  const int n_tiles = a.n_tiles, n_qt = a.n_qt;
   const int HP = a.H >> 1;
 
   if (threadIdx.x == 0) {
@@ -88,6 +126,7 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<512>(&bar->tmem);
+  if (warp == 3 && listed) build_work_list(a.tile_live, a.B, a.n_tiles, wl, wl_hist, lane);
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -99,7 +138,10 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       int ks = 0;
       uint32_t kph = 0, it = 0;
       for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
-        const int hp = item % HP, b = item / HP;
+        const int hp = item % HP;
+        const uint32_t ent = slot_entry(wl, listed, item / HP, n_tiles);
+        const int b = ent & 0xFFFF;
+        const uint32_t live = ent >> 16;
         const int c0 = hp * 2 * D;
         ptx::mbar_wait(&bar->q_empty, (it & 1) ^ 1);
         ptx::mbar_arrive_expect_tx(&bar->q_full, 2 * n_qt * QT_BYTES);
@@ -109,7 +151,8 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             ptx::tma_load_3d(sDO + j * QT_BYTES + h * TQ * 128, &tmDO, &bar->q_full, c0 + h * D, b, j * TQ);
           }
         }
-        for (int i = 0; i < n_tiles; ++i) {
+        for (uint32_t m = live; m; m &= m - 1) {
+          const int i = __ffs(m) - 1;
           ptx::mbar_wait(&bar->kv_empty[ks], kph ^ 1);
           ptx::mbar_arrive_expect_tx(&bar->kv_full[ks], KV_STAGE);
           uint8_t* st = sKV + ks * KV_STAGE;
@@ -146,6 +189,7 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         ptx::umma_commit(&bar->s_ready);
       };
       for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
+        const int n_iter = __popc(slot_entry(wl, listed, item / HP, n_tiles) >> 16) * n_qt;    // i below counts LIVE key tiles
         ptx::mbar_wait(&bar->q_full, it & 1);
         ptx::mbar_wait(&bar->dq_empty, (it & 1) ^ 1);          // previous item's dQ has been read
         // prologue: scores of iteration 0
@@ -214,7 +258,10 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const int x = (warp - 2) * 32 + lane;      // 0..255
     uint32_t it = 0, n_glob = 0, tile_glob = 0;
     for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
-      const int hp = item % HP, b = item / HP;
+      const int hp = item % HP;
+      const uint32_t ent = slot_entry(wl, listed, item / HP, n_tiles);
+      const int b = ent & 0xFFFF;
+      const uint32_t live = ent >> 16;
       // row statistics of the pair: lse2 = lse * log2(e) (+inf beyond T -> P = 0), delta
       asm volatile("bar.sync 3, 256;" ::: "memory");
       {
@@ -227,15 +274,20 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         sStat[which * 128 + h * 64 + t] = v;
       }
       asm volatile("bar.sync 3, 256;" ::: "memory");
-      uint32_t valid = 0;
-      for (int i = 0; i < n_tiles; ++i) {
+      const int n_iter = __popc(live) * n_qt;
+      uint32_t valid = 0;             // bit of key TILE i (not of its position in the live list)
+      for (uint32_t m = live; m; m &= m - 1) {
+        const int i = __ffs(m) - 1;
         const int key = i * TKEYS + quad * 32 + lane;
         bool ok = key < a.S;
         if (ok && a.mask && key < a.mask_S) ok = a.mask[static_cast<long>(b) * a.m_stride_b + key] == 0;
         valid |= static_cast<uint32_t>(ok) << i;
       }
+      uint32_t mleft = live;
       for (int n = 0; n < n_iter; ++n, ++n_glob) {
-        const int i = n / n_qt, j = n - i * n_qt;
+        const int j = n % n_qt;
+        const int i = __ffs(mleft) - 1;                      // key tile of this iteration
+        if (j == n_qt - 1) mleft &= mleft - 1;
         const float* lse2 = sStat + hd * 64 + j * 32;
         const float* dl = sStat + 128 + hd * 64 + j * 32;
         ptx::mbar_wait(&bar->s_ready, n_glob & 1);
@@ -255,7 +307,7 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           float p1 = ok ? exp2f(fmaf(__uint_as_float(sv[c + 1]), a.scale_log2e, -lse2[c + 1])) : 0.f;
           // with dropout m (0 or 1/(1-p)): dV uses P.m, dS = scale * P * (m * dP - delta)
           float m0 = 1.f, m1 = 1.f;
-          if (a.drop.thr) {
+          if (DROP) {
             const unsigned long long i0 =
                 ((static_cast<unsigned long long>(b) * a.H + hp * 2 + hd) * a.T + j * TQ + c) * a.S + i * TKEYS + quad * 32 + lane;
             m0 = drop_val(a.drop, i0, 1.f);
@@ -316,6 +368,18 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(&bar->acc_empty);
           ++tile_glob;
+        }
+      }
+      // ---- key tiles that were skipped (all padding): their dK / dV rows are exactly zero
+      for (uint32_t m = ((1u << n_tiles) - 1u) & ~live; m; m &= m - 1) {
+        const int key = (__ffs(m) - 1) * TKEYS + quad * 32 + lane;
+        if (key < a.S) {
+          const long o = static_cast<long>(key) * a.k_stride_s + static_cast<long>(b) * a.k_stride_b + (hp * 2 + hd) * D;
+#pragma unroll
+          for (int c = 0; c < D; c += 8) {
+            *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(a.dv) + o + c) = make_uint4(0, 0, 0, 0);
+            *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(a.dk) + o + c) = make_uint4(0, 0, 0, 0);
+          }
         }
       }
       // ---- dQ^T: rows (h, d) of this quadrant belong to head (quad / 2); this warp takes 16 queries per tile
@@ -397,6 +461,7 @@ int xattn_bwd_tc(const XattnBwd* p, cudaStream_t st) {
   a.m_stride_b = f.m_stride_b;
   a.lse = f.lse; a.delta = p->scratch;
   a.drop = make_drop(f.drop);
+  a.tile_live = f.tile_live;
   a.dq = p->dq; a.q_stride_t = f.q_stride_t; a.q_stride_b = f.q_stride_b;
   a.dk = p->dk; a.dv = p->dv; a.k_stride_s = f.k_stride_s; a.k_stride_b = f.k_stride_b;
   a.B = f.B; a.T = f.T; a.S = f.S; a.H = f.H;
@@ -408,11 +473,13 @@ int xattn_bwd_tc(const XattnBwd* p, cudaStream_t st) {
   a.n_tiles = (f.S + abt::TKEYS - 1) / abt::TKEYS;
   static bool attr = false;
   if (!attr) {
-    TNT_CUDA(cudaFuncSetAttribute(abt::xattn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, abt::SMEM_BYTES));
+    TNT_CUDA(cudaFuncSetAttribute(abt::xattn_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, abt::SMEM_BYTES));
+    TNT_CUDA(cudaFuncSetAttribute(abt::xattn_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, abt::SMEM_BYTES));
     attr = true;
   }
   const int grid = std::min(a.n_items, num_sms());
-  abt::xattn_bwd_tc_kernel<<<grid, abt::kThreads, abt::SMEM_BYTES, st>>>(tmQ, tmDO, tmK, tmV, a);
+  if (a.drop.thr) abt::xattn_bwd_tc_kernel<true><<<grid, abt::kThreads, abt::SMEM_BYTES, st>>>(tmQ, tmDO, tmK, tmV, a);
+  else abt::xattn_bwd_tc_kernel<false><<<grid, abt::kThreads, abt::SMEM_BYTES, st>>>(tmQ, tmDO, tmK, tmV, a);
   TNT_LAUNCHED();
   return TNT_OK;
 }

@@ -32,7 +32,8 @@ constexpr int KV_STAGE = 2 * TKEYS * 128;         // two heads x 128 keys x 128 
 constexpr int P_STAGE = TKEYS * 128;              // 128 keys x 64 (h,q) bf16
 constexpr int MAX_TILES = 7;
 constexpr uint32_t O_COL = 448;
-constexpr int SMEM_BYTES = Q_BYTES + KS * KV_STAGE + VS * KV_STAGE + PS * P_STAGE + 4096 + 2048;
+constexpr int kListBytes = 2048 * 4 + 128 + 1024;  // sorted work list + histogram (+ the alignment slack of the base)
+constexpr int SMEM_BYTES = Q_BYTES + KS * KV_STAGE + VS * KV_STAGE + PS * P_STAGE + 4096 + 2048 + kListBytes;
 
 struct Args {
   float* lse; float scale;
@@ -42,7 +43,42 @@ struct Args {
   float scale_log2e;
   int n_items, n_qt, n_tiles;
   DropSpec drop;                                  // dropout on the probabilities (the normaliser stays un-dropped)
+  const uint32_t* tile_live;                      // optional [B]: bit i set = key tile i of batch row b holds an un-masked key
 };
+
+// Work list in shared memory: entry = batch row | (key tiles to visit) << 16.  Tiles whose keys are all padding contribute
+// exactly 0 and are skipped.  Every CTA sorts the B entries by live-tile count (longest first, counting sort by one warp
+// in the kernel prologue) so that the static item striding hands every CTA a similar amount of work.
+constexpr int kMaxList = 2048;
+__device__ __forceinline__ void build_work_list(const uint32_t* tile_live, int B, int n_tiles, uint32_t* wl, int* hist, int lane) {
+  const uint32_t all = (1u << n_tiles) - 1u;
+  if (lane < 18) hist[lane] = 0;
+  __syncwarp();
+  for (int b = lane; b < B; b += 32) {
+    uint32_t m = tile_live[b] & all;
+    if (!m) m = 1u;                               // a fully masked row still walks one tile (P = 0 -> out = 0)
+    atomicAdd(&hist[__popc(m)], 1);
+  }
+  __syncwarp();
+  if (lane == 0) {
+    int o = 0;
+    for (int c = 17; c >= 0; --c) {
+      const int n = hist[c];
+      hist[c] = o;
+      o += n;
+    }
+  }
+  __syncwarp();
+  for (int b = lane; b < B; b += 32) {
+    uint32_t m = tile_live[b] & all;
+    if (!m) m = 1u;
+    wl[atomicAdd(&hist[__popc(m)], 1)] = static_cast<uint32_t>(b) | (m << 16);
+  }
+}
+// entry of batch slot bi: from the sorted list, or (bi, every tile) when there is none
+__device__ __forceinline__ uint32_t slot_entry(const uint32_t* wl, bool listed, int bi, int n_tiles) {
+  return listed ? wl[bi] : (static_cast<uint32_t>(bi) | (((1u << n_tiles) - 1u) << 16));
+}
 
 struct Bars {
   uint64_t q_full, q_empty, s_ready, s_empty, o_ready, o_empty;
@@ -57,6 +93,7 @@ __device__ __forceinline__ float redux_max(float v) {
 }
 __device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
+template <bool DROP>      // dropout on the probabilities compiled in only for the training step (zero cost for inference)
 __global__ void __launch_bounds__(kThreads, 1)
 xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, Args a) {
@@ -68,9 +105,11 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint8_t* sP = sV + VS * KV_STAGE;
   float* red = reinterpret_cast<float*>(sP + PS * P_STAGE);          // [2 heads][4 quadrants][32] x 2 (max, sum)
   Bars* bar = reinterpret_cast<Bars*>(reinterpret_cast<uint8_t*>(red) + 4096);
+  uint32_t* wl = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(bar) + 2048);
+  int* wl_hist = reinterpret_cast<int*>(wl + kMaxList);
+  const bool listed = a.tile_live != nullptr && a.B <= kMaxList;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_tiles = a.n_tiles;
 
   if (threadIdx.x == 0) {
     ptx::prefetch_tmap(&tmQ);
@@ -88,6 +127,9 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<512>(&bar->tmem);
+  // tile_live was written several launches earlier; every kernel of the stream waits for its predecessor before it
+  // completes, so the data is final although this prologue runs ahead of pdl_wait()
+  if (warp == 3 && listed) build_work_list(a.tile_live, a.B, a.n_tiles, wl, wl_hist, lane);
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -101,20 +143,25 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       int ks = 0, vs = 0;
       uint32_t kph = 0, vph = 0, it = 0;
       for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
-        const int qt = item % a.n_qt, r = item / a.n_qt, hp = r % HP, b = r / HP;
+        const int qt = item % a.n_qt, r = item / a.n_qt, hp = r % HP;
+        const uint32_t ent = slot_entry(wl, listed, r / HP, a.n_tiles);
+        const int b = ent & 0xFFFF;
+        const uint32_t live = ent >> 16;
         const int c0 = hp * 2 * D;
         ptx::mbar_wait(&bar->q_empty, (it & 1) ^ 1);
         ptx::mbar_arrive_expect_tx(&bar->q_full, Q_BYTES);
         ptx::tma_load_3d(sQ, &tmQ, &bar->q_full, c0, b, qt * TQ);
         ptx::tma_load_3d(sQ + TQ * 128, &tmQ, &bar->q_full, c0 + D, b, qt * TQ);
-        for (int i = 0; i < n_tiles; ++i) {
+        for (uint32_t m = live; m; m &= m - 1) {
+          const int i = __ffs(m) - 1;
           ptx::mbar_wait(&bar->k_empty[ks], kph ^ 1);
           ptx::mbar_arrive_expect_tx(&bar->k_full[ks], KV_STAGE);
           ptx::tma_load_3d(sK + ks * KV_STAGE, &tmK, &bar->k_full[ks], c0, b, i * TKEYS);
           ptx::tma_load_3d(sK + ks * KV_STAGE + TKEYS * 128, &tmK, &bar->k_full[ks], c0 + D, b, i * TKEYS);
           if (++ks == KS) { ks = 0; kph ^= 1; }
         }
-        for (int i = 0; i < n_tiles; ++i) {
+        for (uint32_t m = live; m; m &= m - 1) {
+          const int i = __ffs(m) - 1;
           ptx::mbar_wait(&bar->v_empty[vs], vph ^ 1);
           ptx::mbar_arrive_expect_tx(&bar->v_full[vs], KV_STAGE);
           ptx::tma_load_3d(sV + vs * KV_STAGE, &tmV, &bar->v_full[vs], c0, b, i * TKEYS);
@@ -133,11 +180,12 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       uint32_t kph = 0, vph = 0, pph = 0, it = 0;
       for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
         const uint32_t par = it & 1;
+        const int nl = __popc(slot_entry(wl, listed, (item / a.n_qt) / HP, a.n_tiles) >> 16);   // live key tiles: score tile j at TMEM column j*64
         ptx::mbar_wait(&bar->q_full, par);
         ptx::mbar_wait(&bar->s_empty, par ^ 1);            // previous item's scores have been consumed
         ptx::tc_fence_after();
         const uint32_t q_addr = ptx::smem_u32(sQ);
-        for (int i = 0; i < n_tiles; ++i) {
+        for (int i = 0; i < nl; ++i) {
           ptx::mbar_wait(&bar->k_full[ks], kph);
           ptx::tc_fence_after();
           const uint32_t k_addr = ptx::smem_u32(sK + ks * KV_STAGE);
@@ -157,7 +205,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         ptx::umma_commit(&bar->s_ready);
         ptx::mbar_wait(&bar->o_empty, par ^ 1);            // previous item's output has been read
         ptx::tc_fence_after();
-        for (int i = 0; i < n_tiles; ++i) {
+        for (int i = 0; i < nl; ++i) {
           ptx::mbar_wait(&bar->v_full[vs], vph);
           ptx::mbar_wait(&bar->p_ready[ps], pph);
           ptx::tc_fence_after();
@@ -190,14 +238,21 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     uint32_t pph = 0, it = 0;
     for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
       const uint32_t par = it & 1;
-      const int qt = item % a.n_qt, r = item / a.n_qt, hp = r % HP, b = r / HP;
+      const int qt = item % a.n_qt, r = item / a.n_qt, hp = r % HP;
+      const uint32_t ent = slot_entry(wl, listed, r / HP, a.n_tiles);
+      const int b = ent & 0xFFFF;
+      const uint32_t live = ent >> 16;
       // validity of this lane's key in every tile (key-padding mask: multi_head.py:441-449)
-      uint32_t valid = 0;
-      for (int i = 0; i < n_tiles; ++i) {
-        const int key = i * TKEYS + quad * 32 + lane;
-        bool ok = key < a.S;
-        if (ok && a.mask && key < a.mask_S) ok = a.mask[static_cast<long>(b) * a.m_stride_b + key] == 0;
-        valid |= static_cast<uint32_t>(ok) << i;
+      const int nl = __popc(live);
+      uint32_t valid = 0;             // bit j: this lane's key of the j-th LIVE tile takes part
+      {
+        int j = 0;
+        for (uint32_t m = live; m; m &= m - 1, ++j) {
+          const int key = (__ffs(m) - 1) * TKEYS + quad * 32 + lane;
+          bool ok = key < a.S;
+          if (ok && a.mask && key < a.mask_S) ok = a.mask[static_cast<long>(b) * a.m_stride_b + key] == 0;
+          valid |= static_cast<uint32_t>(ok) << j;
+        }
       }
       ptx::mbar_wait(&bar->s_ready, par);
       ptx::tc_fence_after();
@@ -205,7 +260,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       float mx[32];
 #pragma unroll
       for (int c = 0; c < 32; ++c) mx[c] = -INFINITY;
-      for (int i = 0; i < n_tiles; ++i) {
+      for (int i = 0; i < nl; ++i) {
         uint32_t v[32];
         ptx::tmem_ld_32x32(tmem + lane_base + i * 64 + hd * 32, v);
         ptx::tmem_ld_wait();
@@ -235,7 +290,9 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       float ls[32];
 #pragma unroll
       for (int c = 0; c < 32; ++c) ls[c] = 0.f;
-      for (int i = 0; i < n_tiles; ++i) {
+      uint32_t mleft = live;
+      for (int i = 0; i < nl; ++i, mleft &= mleft - 1) {
+        const int tile = __ffs(mleft) - 1;                    // key tile the i-th score tile belongs to
         uint32_t v[32];
         ptx::tmem_ld_32x32(tmem + lane_base + i * 64 + hd * 32, v);
         ptx::tmem_ld_wait();
@@ -247,9 +304,9 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           float p1 = ok ? exp2f(fmaf(__uint_as_float(v[c + 1]), a.scale_log2e, -mx[c + 1])) : 0.f;
           ls[c] += p0;
           ls[c + 1] += p1;
-          if (a.drop.thr) {
+          if (DROP) {
             const unsigned long long i0 =
-                ((static_cast<unsigned long long>(b) * a.H + hp * 2 + hd) * a.T + qt * TQ + c) * a.S + i * TKEYS + quad * 32 + lane;
+                ((static_cast<unsigned long long>(b) * a.H + hp * 2 + hd) * a.T + qt * TQ + c) * a.S + tile * TKEYS + quad * 32 + lane;
             p0 = drop_val(a.drop, i0, p0);
             p1 = drop_val(a.drop, i0 + a.S, p1);
           }
@@ -315,6 +372,21 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 }
 }  // namespace atc
 
+namespace atc {
+__global__ void __launch_bounds__(256) tile_mask_kernel(const uint8_t* mask, long m_stride_b, int B, int S, int mask_S,
+                                                        uint32_t* out) {
+  const int b = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (b < B) tile_bits_row(mask, m_stride_b, b, S, mask_S, out, threadIdx.x & 31);
+}
+}  // namespace atc
+
+int xattn_tile_mask(const uint8_t* mask, long m_stride_b, int B, int S, int mask_S, uint32_t* out, cudaStream_t st) {
+  TNT_CHECK_ARG(mask && out && B > 0 && S >= 0 && S <= 16 * atc::TKEYS, "xattn_tile_mask: bad arguments (S <= 2048)");
+  atc::tile_mask_kernel<<<(B + 7) / 8, 256, 0, st>>>(mask, m_stride_b, B, S, mask_S > 0 ? std::min(mask_S, S) : S, out);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
 bool xattn_tc_supported(const tnt_xattn_params* p) {
   if (p->dtype != TNT_BF16 || p->D != 64 || (p->H & 1) || p->n_extra != 0 || p->weights || p->kv_group > 1) return false;
   if (p->mask_mode != TNT_MASK_NONE && p->mask_mode != TNT_MASK_KEY_PADDING) return false;
@@ -338,18 +410,28 @@ int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st) {
   a.scale_log2e = p->scale * 1.4426950408889634f;
   a.lse = p->lse; a.scale = p->scale;
   a.drop = make_drop(p->drop);
+  a.tile_live = p->tile_live;
   a.n_qt = (p->T + atc::TQ - 1) / atc::TQ;
   a.n_items = p->B * (p->H / 2) * a.n_qt;
   a.n_tiles = (p->S + atc::TKEYS - 1) / atc::TKEYS;
   static bool attr = false;
   if (!attr) {
-    TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
+    TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
+    TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
     attr = true;
   }
   const int grid = std::min(a.n_items, num_sms());
-  TNT_CUDA(launch_pdl(atc::xattn_tc_kernel, dim3(grid), dim3(atc::kThreads), atc::SMEM_BYTES, st, 1, tmQ, tmK, tmV, a));
+  if (a.drop.thr)
+    TNT_CUDA(launch_pdl(atc::xattn_tc_kernel<true>, dim3(grid), dim3(atc::kThreads), atc::SMEM_BYTES, st, 1, tmQ, tmK, tmV, a));
+  else
+    TNT_CUDA(launch_pdl(atc::xattn_tc_kernel<false>, dim3(grid), dim3(atc::kThreads), atc::SMEM_BYTES, st, 1, tmQ, tmK, tmV, a));
   TNT_LAUNCHED();
   return TNT_OK;
 }
 
 }  // namespace tnt
+
+extern "C" int tnt_xattn_tile_mask(const uint8_t* mask, int64_t m_stride_b, int B, int S, int mask_S, uint32_t* out,
+                                   tnt_stream stream) {
+  return tnt::xattn_tile_mask(mask, m_stride_b, B, S, mask_S, out, tnt::as_stream(stream));
+}

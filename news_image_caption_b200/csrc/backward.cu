@@ -35,10 +35,11 @@ __global__ void __launch_bounds__(256) glu_bwd_kernel(const T* raw, long ldraw, 
 
 // ------------------------------------------------------------------------------ column sums
 // block = 32 x 8: threadIdx.x owns 8 consecutive columns, threadIdx.y strides the rows of this block's chunk
-constexpr int kCsRows = 256;
+// rows per CTA are chosen by the host so that the grid covers the GPU about twice (a [2048, 1024] bias gradient ran on 32
+// CTAs with 32 dependent row loads per thread: 19 us; with 32-row chunks 256 CTAs: a few us)
 template <typename T>
 __global__ void __launch_bounds__(256) colsum_kernel(const T* x, long ldx, int M, int N, const int* m_dyn, float* out,
-                                                     int deinterleave, int vec) {
+                                                     int deinterleave, int vec, int kCsRows) {
   __shared__ float red[8][32][8];
   const int Me = m_dyn ? min(M, *m_dyn) : M;
   const int c0 = (blockIdx.x * 32 + threadIdx.x) * 8;
@@ -46,6 +47,7 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* x, long ldx, int M
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (c0 < N) {
     const int rend = min(Me, r0 + kCsRows);
+#pragma unroll 4
     for (int r = r0 + threadIdx.y; r < rend; r += 8) {
       if (vec && c0 + 8 <= N) {
         float v[8];
@@ -278,11 +280,14 @@ int colsum(const void* x, long ldx, int M, int N, const int* m_dyn, float* out, 
   if (!accumulate) TNT_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * N, st));
   if (M == 0) return TNT_OK;
   const int vec = aligned16(x) && ldx % 8 == 0;
-  dim3 grid((N + 255) / 256, (M + kCsRows - 1) / kCsRows), block(32, 8);
+  const int gx = (N + 255) / 256;
+  int rows_per = 256;                                    // multiple of 8; shrink until ~2 CTAs per SM (>= 16 rows each)
+  while (rows_per > 16 && static_cast<long>(gx) * ((M + rows_per - 1) / rows_per) < 2L * num_sms()) rows_per >>= 1;
+  dim3 grid(gx, (M + rows_per - 1) / rows_per), block(32, 8);
   if (dtype == TNT_BF16)
-    colsum_kernel<bf16><<<grid, block, 0, st>>>(static_cast<const bf16*>(x), ldx, M, N, m_dyn, out, deinterleave, vec);
+    colsum_kernel<bf16><<<grid, block, 0, st>>>(static_cast<const bf16*>(x), ldx, M, N, m_dyn, out, deinterleave, vec, rows_per);
   else
-    colsum_kernel<float><<<grid, block, 0, st>>>(static_cast<const float*>(x), ldx, M, N, m_dyn, out, deinterleave, vec);
+    colsum_kernel<float><<<grid, block, 0, st>>>(static_cast<const float*>(x), ldx, M, N, m_dyn, out, deinterleave, vec, rows_per);
   TNT_LAUNCHED();
   return TNT_OK;
 }

@@ -215,4 +215,22 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
   return r;
 }
 
+// bit i of out[b]: key tile i (128 keys) of batch row b holds at least one key that is not padding.  One warp per row.
+__device__ __forceinline__ void tile_bits_row(const uint8_t* mask, long m_stride_b, int b, int S, int mask_S, uint32_t* out, int lane) {
+  uint32_t bits = 0;
+  const uint8_t* mrow = mask + static_cast<long>(b) * m_stride_b;
+  for (int k0 = 0; k0 < S; k0 += 256) {            // 8 independent byte loads per lane in flight
+    bool lv[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int key = k0 + u * 32 + lane;
+      lv[u] = key < S && (key >= mask_S || mrow[key] == 0);
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (__ballot_sync(0xffffffffu, lv[u])) bits |= 1u << ((k0 + u * 32) / 128);
+  }
+  if (lane == 0) out[b] = bits;
+}
+
 }  // namespace tnt

@@ -85,6 +85,7 @@ struct FwdWs {
   void* Xd;                // training with input_dropout: the dropped-out layer input linear1 reads (else NULL)
   void* kv[TNT_MAX_SOURCES];
   float* lse[TNT_MAX_SOURCES];   // training: attention log-sum-exp [B, H, T] per source (NULL: not saved)
+  uint32_t* tile_live[TNT_MAX_SOURCES];   // [B_kv] live 128-key tiles of every context entry (project_kv fills it)
   size_t total;
 };
 // B_kv >= 0: number of context entries the K/V cache holds when it differs from the row batch B (beam search)

@@ -40,10 +40,18 @@ int layernorm(const void* x, void* y, long ld, const float* g, const float* b, i
 }
 // rows S and S+1 of a K/V buffer: the learned bias_k|bias_v row and the all-zero row that
 // add_bias_kv / add_zero_attn append to every source (multi_head.py:355-374, 416-427)
+// CTAs beyond `main_ctas` (8 batch rows each, one warp per row) compute the live-tile bitmask of the source's
+// key-padding mask for the teacher-forced attention kernels (attention_tc.cu) -- no launch of its own.
 template <typename T>
-__global__ void kv_extra_rows_kernel(T* kv, const float* row, int S, int B, int ld) {
+__global__ void __launch_bounds__(256) kv_extra_rows_kernel(T* kv, const float* row, int S, int B, int ld, int main_ctas,
+                                                            const uint8_t* mask, uint32_t* tile_live) {
+  if (static_cast<int>(blockIdx.x) >= main_ctas) {
+    const int b = (blockIdx.x - main_ctas) * 8 + (threadIdx.x >> 5);
+    if (b < B) tile_bits_row(mask, S, b, S + 2, S, tile_live, threadIdx.x & 31);
+    return;
+  }
   const long n = static_cast<long>(B) * ld;
-  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long>(gridDim.x) * blockDim.x) {
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n; i += static_cast<long>(main_ctas) * blockDim.x) {
     const int c = static_cast<int>(i % ld);
     kv[static_cast<long>(S) * n + i] = from_f<T>(row[c]);
     kv[static_cast<long>(S + 1) * n + i] = from_f<T>(0.f);
@@ -70,6 +78,8 @@ FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool
   w.CATln = w.CAT;
   for (size_t s = 0; s < ns; ++s)
     w.kv[s] = with_kv ? take(static_cast<size_t>(S[s] + 2) * (B_kv >= 0 ? B_kv : B) * c.n_layers * 2 * d * E) : nullptr;
+  for (size_t s = 0; s < ns; ++s)
+    w.tile_live[s] = with_kv ? static_cast<uint32_t*>(take(sizeof(uint32_t) * (B_kv >= 0 ? B_kv : B))) : nullptr;
   w.total = off;
   return w;
 }
@@ -82,10 +92,14 @@ int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStre
   const int ldkv = c.n_layers * 2 * c.d;
   for (int s = 0; s < c.n_sources; ++s) {
     const int grid = std::min<long>((static_cast<long>(ctx->B) * ldkv + 255) / 256, 4L * num_sms());
+    const bool scan = w.tile_live[s] && ctx->pad_mask[s] && ctx->S[s] > 0;
+    const int extra = scan ? (ctx->B + 7) / 8 : 0;
     if (c.dtype == TNT_BF16)
-      kv_extra_rows_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<bf16*>(w.kv[s]), D->kvrow[s], ctx->S[s], ctx->B, ldkv);
+      kv_extra_rows_kernel<bf16><<<grid + extra, 256, 0, st>>>(static_cast<bf16*>(w.kv[s]), D->kvrow[s], ctx->S[s], ctx->B, ldkv,
+                                                               grid, ctx->pad_mask[s], w.tile_live[s]);
     else
-      kv_extra_rows_kernel<float><<<grid, 256, 0, st>>>(static_cast<float*>(w.kv[s]), D->kvrow[s], ctx->S[s], ctx->B, ldkv);
+      kv_extra_rows_kernel<float><<<grid + extra, 256, 0, st>>>(static_cast<float*>(w.kv[s]), D->kvrow[s], ctx->S[s], ctx->B, ldkv,
+                                                                grid, ctx->pad_mask[s], w.tile_live[s]);
     TNT_LAUNCHED();
     if (ctx->S[s] == 0) continue;
     TNT_CHECK_ARG(ctx->memory[s], "decoder: context '%s' missing", c.source_names[s]);
@@ -168,6 +182,8 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     ap.mask_S = ctx->S[s];
     ap.kv_group = kv_group;
     ap.drop = drop_site(dr, dr ? dr->attention_dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_ATTN_PROB + s));
+    static const bool tile_skip = [] { const char* e = getenv("TNT_TILE_SKIP"); return !(e && e[0] == '0'); }();
+    ap.tile_live = (tile_skip && kv_group <= 1 && ap.mask_mode == TNT_MASK_KEY_PADDING) ? w.tile_live[s] : nullptr;
     if (ctx->S[s] == 0) ap.mask_mode = TNT_MASK_NONE;
     ap.scale = 1.0f / sqrtf(static_cast<float>(d / H));
     ap.dtype = dt;

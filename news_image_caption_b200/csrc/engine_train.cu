@@ -30,6 +30,7 @@ struct TrainWs {
   LayerAct act[TNT_MAX_LAYERS];
   void* kv[TNT_MAX_SOURCES];
   void* dkv[TNT_MAX_SOURCES];
+  uint32_t* tile_live[TNT_MAX_SOURCES];        // [B] live 128-key tiles per context entry
   void *Xbt, *dXbt;                            // decoder output / its gradient in B x T row order
   void *gA, *gB, *gC, *gD;                     // [N, d] gradient ping-pong buffers
   void *dQ, *dAO, *dCAT, *dCATp;               // [N, ns*d]
@@ -71,6 +72,7 @@ TrainWs carve_train(const tnt_decoder* D, int B, int T, const int* S, void* ws) 
     const size_t bytes = static_cast<size_t>(S[s] + 2) * B * L * 2 * d * E;
     w.kv[s] = take(bytes);
     w.dkv[s] = take(bytes);
+    w.tile_live[s] = static_cast<uint32_t*>(take(sizeof(uint32_t) * B));
     max_kdim = std::max<size_t>(max_kdim, c.source_dim[s]);
   }
   w.Xbt = take(N * d * E); w.dXbt = take(N * d * E);
@@ -171,6 +173,7 @@ FwdWs layer_ws(const TrainWs& w, int l, int ns) {
   for (int s = 0; s < ns; ++s) {
     f.kv[s] = w.kv[s];
     f.lse[s] = a.lse[s];
+    f.tile_live[s] = w.tile_live[s];
   }
   return f;
 }
@@ -199,6 +202,7 @@ tnt_xattn_params attn_params(const tnt_decoder* D, const tnt_contexts* ctx, cons
   ap.dtype = c.dtype;
   ap.lse = a.lse[s];
   ap.drop = drop_site(dr, dr ? dr->attention_dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_ATTN_PROB + s));
+  ap.tile_live = (ap.mask_mode == TNT_MASK_KEY_PADDING) ? w.tile_live[s] : nullptr;
   return ap;
 }
 

@@ -181,7 +181,7 @@ def layernorm_bwd(x, dy, gamma, eps=1e-5):
 
 
 def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=None, need_weights=False, mask_S=0,
-          lse=None, drop=None):
+          lse=None, drop=None, tile_live=None):
     """q [T,B,E], k/v [S,B,E] (projected) -> out [T,B,E] (+ head-averaged weights [B,T,S+n_extra]).
     pad_mask [B,S] bool True=pad (tell);  v2_mask [B,1|T,S] 'visible' mask (final*), 0 -> -1e9."""
     q, k, v = _cuda(q).contiguous(), k.contiguous(), v.contiguous()
@@ -218,11 +218,22 @@ def xattn(q, k, v, H, scale, pad_mask=None, bias_k=None, bias_v=None, v2_mask=No
         p.lse = lse.data_ptr()
     p.B, p.T, p.S, p.H, p.D, p.n_extra, p.scale, p.dtype = B, T, S, H, E // H, n_extra, scale, _code(q)
     p.drop = _drop(drop)
+    if tile_live is not None:
+        p.tile_live = tile_live.data_ptr()
     _lib.check(_lib.lib().tnt_xattn_fwd(C.byref(p), _st()), 'tnt_xattn_fwd')
     return out, w
 
 
-def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=0, lse=None, drop=None):
+def xattn_tile_mask(pad_mask, S, mask_S=0):
+    """pad_mask [B, >= mask_S] bool -> int32 [B]: bit i = keys [128 i, 128 i + 128) of row b hold an un-masked key."""
+    m = _cuda(pad_mask).to(torch.bool).contiguous()
+    out = torch.empty(m.shape[0], dtype=torch.int32, device=m.device)
+    _lib.check(_lib.lib().tnt_xattn_tile_mask(m.data_ptr(), m.shape[1], m.shape[0], S, mask_S, out.data_ptr(), _st()),
+               'tnt_xattn_tile_mask')
+    return out
+
+
+def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=0, lse=None, drop=None, tile_live=None):
     """Backward of `xattn` (n_extra = 0: extra rows are ordinary k / v rows).  Returns (dq, dk, dv)."""
     q, k, v, out, dout = [_cuda(t).contiguous() for t in (q, k, v, out, dout)]
     T, B, E = q.shape
@@ -247,6 +258,8 @@ def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=
         p.m_stride_t = S if m.shape[1] > 1 else 0
     p.B, p.T, p.S, p.H, p.D, p.n_extra, p.scale, p.dtype = B, T, S, H, E // H, 0, scale, _code(q)
     p.drop = _drop(drop)
+    if tile_live is not None:
+        p.tile_live = tile_live.data_ptr()
     if lse is not None:
         p.lse = lse.data_ptr()
     L = _lib.lib()

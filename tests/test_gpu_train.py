@@ -96,6 +96,42 @@ def test_xattn_probability_dropout(ops, T, S, B, H, D, dtype):
     assert rel_err(dq, gq) < tol and rel_err(dk, gk) < tol and rel_err(dv, gv) < tol
 
 
+def test_xattn_skips_all_padding_key_tiles(ops):
+    """The tcgen05 forward / backward visit only the 128-key tiles that hold a live key (tnt_xattn_tile_mask): same
+    numbers as visiting every tile, and as fp64, for suffix padding, a dead tile in the MIDDLE and a fully masked row."""
+    g = torch.Generator().manual_seed(31)
+    T, S, B, H, D = 32, 514, 6, 4, 64
+    E = H * D
+    q, k, v, do = [torch.randn(n, B, E, generator=g).bfloat16() for n in (T, S, S, T)]
+    pad = torch.zeros(B, S - 2, dtype=torch.bool)
+    pad[0, 130:] = True                    # tiles 2, 3 dead (tile 4 holds the 2 extra keys)
+    pad[1, 300:] = True
+    pad[2, 128:256] = True                 # a dead tile in the middle
+    pad[3, :] = True                       # only the extra keys remain
+    pad[4, 5:] = True
+    tl = ops.xattn_tile_mask(pad.cuda(), S, S - 2)
+    assert tl.cpu().tolist() == [0b10011, 0b10111, 0b11101, 0b10000, 0b10001, 0b11111]
+    scale = D ** -0.5
+    lse0 = torch.empty(B, H, T, device='cuda')
+    lse1 = torch.empty(B, H, T, device='cuda')
+    full, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, scale, pad_mask=pad.cuda(), mask_S=S - 2, lse=lse0)
+    skip, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, scale, pad_mask=pad.cuda(), mask_S=S - 2, lse=lse1, tile_live=tl)
+    assert torch.equal(full, skip) and torch.equal(lse0, lse1)
+    qd, kd, vd = [t.double().requires_grad_(True) for t in (q, k, v)]
+    s = torch.einsum('tbhd,sbhd->bhts', qd.view(T, B, H, D), kd.view(S, B, H, D)) * scale
+    fm = torch.cat([pad, torch.zeros(B, 2, dtype=torch.bool)], 1)
+    s = s.masked_fill(fm[:, None, None, :], float('-inf'))
+    o = torch.einsum('bhts,sbhd->tbhd', torch.softmax(s, -1), vd.view(S, B, H, D)).reshape(T, B, E)
+    gq, gk, gv = torch.autograd.grad(o, [qd, kd, vd], do.double())
+    assert rel_err(skip, o.detach()) < 3e-2
+    a = ops.xattn_bwd(q.cuda(), k.cuda(), v.cuda(), full, do.cuda(), H, scale, pad_mask=pad.cuda(), mask_S=S - 2, lse=lse0)
+    b = ops.xattn_bwd(q.cuda(), k.cuda(), v.cuda(), full, do.cuda(), H, scale, pad_mask=pad.cuda(), mask_S=S - 2, lse=lse0,
+                      tile_live=tl)
+    for x, y, z in zip(a, b, (gq, gk, gv)):
+        assert rel_err(y, x) < 1e-6 and rel_err(y, z) < 3e-2
+    assert float(b[1][:, 3][:S - 2].abs().max()) == 0.0          # masked keys receive exactly zero gradient
+
+
 @pytest.mark.parametrize('T,S,B,H', [(32, 514, 3, 4), (7, 130, 2, 2), (40, 51, 5, 16), (64, 1000, 2, 2)])
 def test_xattn_backward_tcgen05(ops, T, S, B, H):
     """The tcgen05 / TMEM backward kernel (bf16, D = 64, T <= 64, lse saved by the forward) against fp64

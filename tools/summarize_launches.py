@@ -22,7 +22,8 @@ def main():
     rows = list(csv.DictReader(lines))
     names = [short(r['Kernel Name']) for r in rows]
     ns = [float(r['Metric Value']) for r in rows]
-    starts = [i for i, n in enumerate(names) if marker in n and (i == 0 or marker not in names[i - 2])]
+    # a step starts at a marker launch that has no other marker launch among the 4 launches before it (one per source)
+    starts = [i for i, n in enumerate(names) if marker in n and not any(marker in m for m in names[max(0, i - 4):i])]
     if len(starts) < 2:
         print('fewer than two steps found')
         return
