@@ -105,6 +105,31 @@ def load_tell():
     return ns
 
 
+def load_faces_objects_model_class():
+    """The unmodified `TransformerFacesObjectModel` class (ttl/tell/models/transformer_faces_objects.py) with the
+    AllenNLP / pycocoevalcap base classes stubbed: only its `_forward` (context assembly, :312-397) is used, on an
+    instance whose RoBERTa / ResNet members are replaced by fakes (the hubs are not reachable here)."""
+    install_stubs()
+    import torch.nn as nn
+
+    class Model(nn.Module):
+        @classmethod
+        def register(cls, name, *a, **k):
+            return lambda c: c
+
+    if 'allennlp.models.model' not in sys.modules:
+        _mod('allennlp.data.vocabulary', Vocabulary=sys.modules['allennlp.data'].Vocabulary)
+        _mod('allennlp.models')
+        _mod('allennlp.models.model', Model=Model)
+        _mod('allennlp.nn')
+        _mod('allennlp.nn.initializers', InitializerApplicator=object)
+        _mod('pycocoevalcap')
+        _mod('pycocoevalcap.bleu')
+        _mod('pycocoevalcap.bleu.bleu_scorer', BleuScorer=object)
+    mod = importlib.import_module('tell.models.transformer_faces_objects')
+    return mod.TransformerFacesObjectModel
+
+
 def load_final_v2(variant='final_roberta2'):
     path = os.path.join(REF_ROOT, variant)
     name = 'ref_transformer_v2_' + variant

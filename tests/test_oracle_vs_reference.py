@@ -173,6 +173,52 @@ def test_pointer_decoder_matches_reference():
     torch.set_grad_enabled(True)
 
 
+@pytest.mark.parametrize('weigh_bert', [True, False])
+def test_context_assembly_matches_reference(weigh_bert):
+    """Row f2: the UNMODIFIED `TransformerFacesObjectModel._forward` (transformer_faces_objects.py:312-397) -- RoBERTa
+    hidden-layer mix with softmax(bert_weight), NaN face / object rows -> masks, the transposes and the target shift --
+    run on an instance whose RoBERTa / ResNet members are fakes (the hubs are unreachable), against the oracle's
+    context_mix / nan_padding_mask."""
+    torch.set_grad_enabled(False)
+    Cls = ri.load_faces_objects_model_class()
+    g = torch.Generator().manual_seed(5)
+    B, S, E, n_hid = 3, 11, 16, 25
+    hid = [torch.randn(B, S, E, generator=g) for _ in range(n_hid)]
+    feat = torch.randn(B, 2048, 7, 7, generator=g).abs()
+
+    class FakeRoberta:
+        def extract_features(self, ids, return_all_hiddens=False):
+            assert return_all_hiddens
+            return hid
+
+    m = object.__new__(Cls)
+    torch.nn.Module.__init__(m)
+    m.index, m.padding_idx, m.weigh_bert = 'roberta', 1, weigh_bert
+    m.bert_weight = torch.nn.Parameter(torch.randn(n_hid, generator=g))
+    object.__setattr__(m, 'roberta', FakeRoberta())
+    object.__setattr__(m, 'resnet', lambda image: feat)
+    art_ids = torch.randint(3, 100, (B, S), generator=g)
+    art_ids[0, 7:] = 1
+    cap = torch.randint(3, 100, (B, 9), generator=g)
+    faces = torch.randn(B, 4, 512, generator=g)
+    faces[0, 2:] = float('nan')
+    faces[1, :] = float('nan')
+    objs = torch.randn(B, 6, 2048, generator=g)
+    objs[2, 1:] = float('nan')
+    cap_ids, tgt_ids, ctx = m._forward({'roberta': art_ids}, torch.zeros(B, 3, 224, 224), {'roberta': cap.clone()},
+                                       faces.clone(), objs.clone())
+    assert torch.equal(cap_ids, cap[:, :-1]) and torch.equal(tgt_ids, cap[:, 1:])
+    want_article = O.context_mix(hid, m.bert_weight) if weigh_bert else hid[-1].transpose(0, 1)
+    close(want_article, ctx['article'], 1e-6)
+    assert torch.equal(ctx['article_mask'], art_ids == 1)
+    assert torch.equal(ctx['image'], feat.permute(0, 2, 3, 1).reshape(B, 49, 2048).transpose(0, 1))
+    assert ctx['image_mask'].shape == (B, 49) and not ctx['image_mask'].any()
+    for key, src in (('faces', faces), ('obj', objs)):
+        e, mk = O.nan_padding_mask(src)
+        assert torch.equal(e, ctx[key]) and torch.equal(mk, ctx[key + '_mask'])
+    torch.set_grad_enabled(True)
+
+
 def test_v2_other_variant():
     torch.set_grad_enabled(False)
     tv = ri.load_final_v2('final_roberta2')
