@@ -161,6 +161,154 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_kernel(tnt_dynconv_param
   }
 }
 
+// ------------------------------------------------------------------------------ forward on tensor cores (bf16)
+// The SIMT forward is bound by its FMA / shared-memory instruction stream (K = 31: 31 FMAs per output, 15 % of the HBM
+// roofline), not by HBM.  This form does what the reference's own fast path does (dynamic.py:285-336, "band matrices"):
+// per (b, head) Y[32 x 64] = W_band[32 x KW] . X_window[KW x 64] -- on warp-level tensor-core MMAs (m16n8k16, bf16 in,
+// fp32 accumulate): the tile is far too small for a tcgen05 (128-row) instruction, and the kernel's job is to get out
+// of the way of the HBM stream.  CTA = (b, 4 heads = 256 channels, 32 timesteps), 8 warps, warp = (head, 32 channels).
+//   smem: window rows [KW][256] bf16 (row stride padded by 16 B against ldmatrix bank conflicts), taps fp32 (soft-max,
+//   dropout), band matrices [4][32][KW] bf16.  Zero k-tiles of the band are skipped (3 of 4 remain at K = 31).
+namespace tcv {
+constexpr int TT = 32, HG = 4, R = 64, CC = HG * R;
+constexpr int XS_STRIDE = CC * 2 + 16;                    // bytes per window row
+
+__device__ __forceinline__ uint32_t ptx_smem(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// All global reads of the CTA (window rows, raw tap logits) are issued as cp.async up front: the earlier version's
+// staging loops (load -> store per iteration) serialised one memory latency per iteration and per thread, which --
+// not the arithmetic -- was what kept the kernel at 15 % of the HBM roofline.
+__global__ void __launch_bounds__(kThreads) dynconv_fwd_tc_kernel(tnt_dynconv_params p, int KW, DropSpec dr) {
+  pdl_wait();
+  extern __shared__ __align__(16) uint8_t smb[];
+  const int K = p.K, B = p.B;
+  const int b = blockIdx.x, c0 = blockIdx.y * CC, t0 = blockIdx.z * TT;
+  const int TTl = min(TT, p.T - t0);
+  const int rows = TTl + K - 1;
+  const int AS = KW * 2 + 16;                            // bytes per band-matrix row
+  const int HK = HG * K;                                 // tap logits of the CTA's heads per timestep (even)
+  uint8_t* xs = smb;                                     // [KW][XS_STRIDE]
+  uint8_t* As = xs + KW * XS_STRIDE;                     // [HG][TT][AS]
+  bf16* lraw = reinterpret_cast<bf16*>(As + HG * TT * AS);     // [TT][HK] raw tap logits
+  const bf16* x = reinterpret_cast<const bf16*>(p.x);
+  const bf16* hist = reinterpret_cast<const bf16*>(p.hist);
+  const bf16* lg = reinterpret_cast<const bf16*>(p.logits);
+  bf16* y = reinterpret_cast<bf16*>(p.y);
+  constexpr int nv = CC / 8;
+  const int h0 = c0 / R;
+
+  const uint32_t xs_s = ptx_smem(xs), lraw_s = ptx_smem(lraw);
+  for (int i = threadIdx.x; i < KW * nv; i += kThreads) {
+    const int r = i / nv, vc = i - r * nv;
+    const int ts = t0 - (K - 1) + r;
+    const uint32_t d = xs_s + r * XS_STRIDE + vc * 16;
+    if (r < rows && ts >= 0) cp_async16(d, x + (static_cast<long>(ts) * B + b) * p.ldx + c0 + vc * 8);
+    else if (r < rows && hist && p.hist_len + ts >= 0) cp_async16(d, hist + (static_cast<long>(p.hist_len + ts) * B + b) * p.C + c0 + vc * 8);
+    else *reinterpret_cast<uint4*>(xs + r * XS_STRIDE + vc * 16) = make_uint4(0, 0, 0, 0);
+  }
+  {
+    const int wpr = HK >> 1;                             // 4-byte words per timestep
+    for (int i = threadIdx.x; i < TTl * wpr; i += kThreads) {
+      const int r = i / wpr, wd = i - r * wpr;
+      cp_async4(lraw_s + (r * HK + 2 * wd) * 2, lg + (static_cast<long>(t0 + r) * B + b) * p.ldl + h0 * K + 2 * wd);
+    }
+  }
+  for (int i = threadIdx.x; i < (HG * TT * AS) / 16; i += kThreads) reinterpret_cast<uint4*>(As)[i] = make_uint4(0, 0, 0, 0);
+  cp_async_wait_all();
+  __syncthreads();
+  // soft-max of the K taps of every (t, head) and its row of the band matrix: A[hl][t][t + j] = w_j (window row c holds
+  // time t0 - (K-1) + c, so output t reads rows t .. t+K-1); two threads per (t, head) would not pay: 128 x K exps
+  {
+    const int i = threadIdx.x >> 1, half = threadIdx.x & 1;          // TT * HG = 128 (t, head) rows, two threads each
+    const int t_raw = i / HG, hl = i - t_raw * HG;
+    const bool on = t_raw < TTl;                                       // rows beyond the tile: compute on row 0, write nothing
+    const int t = on ? t_raw : 0;
+    {
+      const bf16* l = lraw + t * HK + hl * K;
+      float m = -INFINITY;
+      for (int j = half; j < K; j += 2) m = fmaxf(m, __bfloat162float(l[j]));
+      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+      float sum = 0.f;
+      for (int j = half; j < K; j += 2) sum += __expf(__bfloat162float(l[j]) - m);
+      sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+      const float inv = 1.f / sum;
+      bf16* arow = reinterpret_cast<bf16*>(As + (hl * TT + t) * AS) + t;
+      const unsigned long long i0 = ((static_cast<unsigned long long>(t0 + t) * B + b) * p.H + h0 + hl) * K;
+      for (int j = half; j < K; j += 2) {
+        float w = __expf(__bfloat162float(l[j]) - m) * inv;
+        if (dr.thr) w = drop_val(dr, i0 + j, w);
+        if (on) arow[j] = __float2bfloat16_rn(w);
+      }
+    }
+  }
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int hl = warp >> 1, chb = (warp & 1) * 32;       // channels [hl*64 + chb, +32) of the CTA's 256
+  float acc[2][4][4];
+#pragma unroll
+  for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[mi][nt][e] = 0.f;
+  const uint32_t a_base = ptx_smem(As + hl * TT * AS) + ((lane & 7) + 8 * ((lane >> 3) & 1)) * AS + 16 * (lane >> 4);
+  const uint32_t b_base = ptx_smem(xs) + ((lane & 7) + 8 * ((lane >> 3) & 1)) * XS_STRIDE + (hl * R + chb + 8 * (lane >> 4)) * 2;
+  const int nkt = KW >> 4;
+#pragma unroll
+  for (int mi = 0; mi < 2; ++mi) {
+    const int kt_hi = min(nkt, ((16 * mi + 15 + K - 1) >> 4) + 1);
+    for (int kt = mi; kt < kt_hi; ++kt) {
+      uint32_t a[4];
+      ldsm_x4(a, a_base + mi * 16 * AS + kt * 32);
+#pragma unroll
+      for (int jp = 0; jp < 2; ++jp) {
+        uint32_t bq[4];
+        ldsm_x4_trans(bq, b_base + kt * 16 * XS_STRIDE + jp * 32);
+        mma_bf16(acc[mi][2 * jp], a, bq[0], bq[1]);
+        mma_bf16(acc[mi][2 * jp + 1], a, bq[2], bq[3]);
+      }
+    }
+  }
+  __syncthreads();                                       // every warp is done with the window: reuse it for the output tile
+#pragma unroll
+  for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      const int col = hl * R + chb + nt * 8 + 2 * (lane & 3);
+      const int r0 = mi * 16 + (lane >> 2);
+      *reinterpret_cast<uint32_t*>(xs + r0 * XS_STRIDE + col * 2) = pack_bf16x2(acc[mi][nt][0], acc[mi][nt][1]);
+      *reinterpret_cast<uint32_t*>(xs + (r0 + 8) * XS_STRIDE + col * 2) = pack_bf16x2(acc[mi][nt][2], acc[mi][nt][3]);
+    }
+  __syncthreads();
+  for (int i = threadIdx.x; i < TTl * nv; i += kThreads) {
+    const int t = i / nv, vc = i - t * nv;
+    *reinterpret_cast<uint4*>(y + (static_cast<long>(t0 + t) * B + b) * p.ldy + c0 + vc * 8) =
+        *reinterpret_cast<const uint4*>(xs + t * XS_STRIDE + vc * 16);
+  }
+}
+}  // namespace tcv
+
 // ------------------------------------------------------------------------------ single step
 // ring [K-1][B][C]; slot of step s = s mod (K-1).  One thread = 8 channels of one batch row.
 template <typename T>
@@ -334,6 +482,18 @@ extern "C" int tnt_dynconv_fwd(const tnt_dynconv_params* p, tnt_stream stream) {
   dim3 grid(p->B, ngroups, (p->T + kTT - 1) / kTT);
   TNT_CHECK_ARG(p->drop.p >= 0.f && p->drop.p < 1.f, "dynconv: dropout p = %f", p->drop.p);
   const DropSpec dr = make_drop(p->drop);
+  static const bool tc_on = [] { const char* e = getenv("TNT_DYNCONV_TC"); return !(e && e[0] == '0'); }();
+  if (tc_on && p->dtype == TNT_BF16 && p->C / p->H == tcv::R && p->C % tcv::CC == 0 && p->K <= 33 && p->ldy % 8 == 0 && p->ldl % 2 == 0 &&
+      (reinterpret_cast<uintptr_t>(p->logits) & 3) == 0) {
+    const int KW = (tcv::TT + p->K - 1 + 15) & ~15;
+    const size_t sm = static_cast<size_t>(KW) * tcv::XS_STRIDE + static_cast<size_t>(tcv::HG) * tcv::TT * (KW * 2 + 16) +
+                      static_cast<size_t>(tcv::TT) * tcv::HG * p->K * 2;
+    TNT_TRY(set_smem(tcv::dynconv_fwd_tc_kernel, sm));
+    dim3 g2(p->B, p->C / tcv::CC, (p->T + tcv::TT - 1) / tcv::TT);
+    TNT_CUDA(launch_pdl(tcv::dynconv_fwd_tc_kernel, g2, dim3(kThreads), sm, as_stream(stream), 1, *p, KW, dr));
+    TNT_LAUNCHED();
+    return TNT_OK;
+  }
   if (p->dtype == TNT_BF16) {
     TNT_TRY(set_smem(dynconv_fwd_kernel<bf16>, smem));
     TNT_CUDA(launch_pdl(dynconv_fwd_kernel<bf16>, grid, dim3(kThreads), smem, as_stream(stream), 1, *p, CC, HG, dr));
