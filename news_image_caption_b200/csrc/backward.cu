@@ -281,8 +281,9 @@ int colsum(const void* x, long ldx, int M, int N, const int* m_dyn, float* out, 
   if (M == 0) return TNT_OK;
   const int vec = aligned16(x) && ldx % 8 == 0;
   const int gx = (N + 255) / 256;
-  int rows_per = 256;                                    // multiple of 8; shrink until ~2 CTAs per SM (>= 16 rows each)
-  while (rows_per > 16 && static_cast<long>(gx) * ((M + rows_per - 1) / rows_per) < 2L * num_sms()) rows_per >>= 1;
+  int rows_per = 256;                                    // multiple of 8; shrink until ~2 CTAs per SM (>= 32 rows each:
+                                                         // 4 independent loads per thread, <= M/32 atomics per column)
+  while (rows_per > 32 && static_cast<long>(gx) * ((M + rows_per - 1) / rows_per) < 2L * num_sms()) rows_per >>= 1;
   dim3 grid(gx, (M + rows_per - 1) / rows_per), block(32, 8);
   if (dtype == TNT_BF16)
     colsum_kernel<bf16><<<grid, block, 0, st>>>(static_cast<const bf16*>(x), ldx, M, N, m_dyn, out, deinterleave, vec, rows_per);

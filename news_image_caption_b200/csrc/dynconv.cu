@@ -307,6 +307,196 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_tc_kernel(tnt_dynconv_pa
         *reinterpret_cast<const uint4*>(xs + t * XS_STRIDE + vc * 16);
   }
 }
+
+// ------------------------------------------------------------------------------ backward on tensor cores (bf16)
+// Same tiling as the forward.  Windows: XW rows = times t0-(K-1) .. t0+31 (conv inputs), DW rows = times t0 .. t0+31+(K-1)
+// (output gradients; the tile's inputs feed K-1 later outputs), raw tap logits of the DW rows.
+//   dx [32 x 64]  = A_dx [32 x KW] . DW [KW x 64],  A_dx[s][r] = w_dropped[r][j = s + (K-1) - r]        (value path)
+//   P  [32 x KW]  = dY [32 x 64] . XW^T,             dw[t][j] = P[t][t + j] (x dropout mask)              (tap path)
+//   dlogits[t][j] = w_j (dw_j - sum_i w_i dw_i)      soft-max backward with the un-dropped w (recomputed from the raw
+//                                                     logits and the per-row (max, 1/sum) kept from the first pass)
+__global__ void __launch_bounds__(kThreads) dynconv_bwd_tc_kernel(tnt_dynconv_bwd_params p, int KW, DropSpec dr) {
+  extern __shared__ __align__(16) uint8_t smb[];
+  const int K = p.K, B = p.B, KM = K - 1;
+  const int b = blockIdx.x, c0 = blockIdx.y * CC, t0 = blockIdx.z * TT;
+  const int TTl = min(TT, p.T - t0);
+  const int rows_x = TTl + KM;                           // XW rows that hold data
+  const int rows_y = min(TT + KM, p.T - t0);             // DW / logits rows that exist
+  const int AS = KW * 2 + 16;
+  const int HK = HG * K;
+  uint8_t* xw = smb;                                     // [KW][XS_STRIDE]
+  uint8_t* dw = xw + KW * XS_STRIDE;                     // [KW][XS_STRIDE]
+  uint8_t* As = dw + KW * XS_STRIDE;                     // [HG][TT][AS]  band matrix, later dws fp32 [TT][HG][K]
+  bf16* lraw = reinterpret_cast<bf16*>(As + HG * TT * AS);     // [KW][HK] raw logits, later dlogits of rows < 32
+  float2* stat = reinterpret_cast<float2*>(reinterpret_cast<uint8_t*>(lraw) + ((KW * HK * 2 + 15) & ~15));   // [KW][HG] (max, 1/sum)
+  const bf16* x = reinterpret_cast<const bf16*>(p.x);
+  const bf16* dy = reinterpret_cast<const bf16*>(p.dy);
+  const bf16* lg = reinterpret_cast<const bf16*>(p.logits);
+  constexpr int nv = CC / 8;
+  const int h0 = c0 / R;
+
+  const uint32_t xw_s = ptx_smem(xw), dw_s = ptx_smem(dw), lraw_s = ptx_smem(lraw);
+  for (int i = threadIdx.x; i < KW * nv; i += kThreads) {
+    const int r = i / nv, vc = i - r * nv;
+    const int ts = t0 - KM + r;
+    if (r < rows_x && ts >= 0) cp_async16(xw_s + r * XS_STRIDE + vc * 16, x + (static_cast<long>(ts) * B + b) * p.ldx + c0 + vc * 8);
+    else *reinterpret_cast<uint4*>(xw + r * XS_STRIDE + vc * 16) = make_uint4(0, 0, 0, 0);
+    if (r < rows_y) cp_async16(dw_s + r * XS_STRIDE + vc * 16, dy + (static_cast<long>(t0 + r) * B + b) * p.lddy + c0 + vc * 8);
+    else *reinterpret_cast<uint4*>(dw + r * XS_STRIDE + vc * 16) = make_uint4(0, 0, 0, 0);
+  }
+  {
+    const int wpr = HK >> 1;
+    for (int i = threadIdx.x; i < rows_y * wpr; i += kThreads) {
+      const int r = i / wpr, wd = i - r * wpr;
+      cp_async4(lraw_s + (r * HK + 2 * wd) * 2, lg + (static_cast<long>(t0 + r) * B + b) * p.ldl + h0 * K + 2 * wd);
+    }
+  }
+  for (int i = threadIdx.x; i < (HG * TT * AS) / 16; i += kThreads) reinterpret_cast<uint4*>(As)[i] = make_uint4(0, 0, 0, 0);
+  cp_async_wait_all();
+  __syncthreads();
+  // pass 1: soft-max statistics of every (DW row, head) and its column of the dx band matrix
+  for (int i = threadIdx.x; i < rows_y * HG; i += kThreads) {
+    const int r = i / HG, hl = i - r * HG;
+    const bf16* l = lraw + r * HK + hl * K;
+    float m = -INFINITY;
+    for (int j = 0; j < K; ++j) m = fmaxf(m, __bfloat162float(l[j]));
+    float sum = 0.f;
+    for (int j = 0; j < K; ++j) sum += __expf(__bfloat162float(l[j]) - m);
+    const float inv = 1.f / sum;
+    stat[r * HG + hl] = make_float2(m, inv);
+    const unsigned long long i0 = ((static_cast<unsigned long long>(t0 + r) * B + b) * p.H + h0 + hl) * K;
+    const int j_lo = max(0, KM - r), j_hi = min(K - 1, TT - 1 + KM - r);   // input row s = r - (K-1) + j of the tile, 0 <= s < 32
+    for (int j = j_lo; j <= j_hi; ++j) {
+      const int sidx = r - KM + j;
+      float w = __expf(__bfloat162float(l[j]) - m) * inv;
+      if (dr.thr) w = drop_val(dr, i0 + j, w);
+      *reinterpret_cast<bf16*>(As + (hl * TT + sidx) * AS + r * 2) = __float2bfloat16_rn(w);
+    }
+  }
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int hl = warp >> 1, half = warp & 1, chb = half * 32;
+  const int lrow = (lane & 7) + 8 * ((lane >> 3) & 1);
+  // ---- dx = A_dx . DW (the forward's MMA structure with the gradient window)
+  float accx[2][4][4];
+#pragma unroll
+  for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) accx[mi][nt][e] = 0.f;
+  {
+    const uint32_t a_base = ptx_smem(As + hl * TT * AS) + lrow * AS + 16 * (lane >> 4);
+    const uint32_t b_base = dw_s + lrow * XS_STRIDE + (hl * R + chb + 8 * (lane >> 4)) * 2;
+    const int nkt = KW >> 4;
+#pragma unroll
+    for (int mi = 0; mi < 2; ++mi) {
+      const int kt_hi = min(nkt, ((16 * mi + 15 + KM) >> 4) + 1);
+      for (int kt = mi; kt < kt_hi; ++kt) {
+        uint32_t a[4];
+        ldsm_x4(a, a_base + mi * 16 * AS + kt * 32);
+#pragma unroll
+        for (int jp = 0; jp < 2; ++jp) {
+          uint32_t bq[4];
+          ldsm_x4_trans(bq, b_base + kt * 16 * XS_STRIDE + jp * 32);
+          mma_bf16(accx[mi][2 * jp], a, bq[0], bq[1]);
+          mma_bf16(accx[mi][2 * jp + 1], a, bq[2], bq[3]);
+        }
+      }
+    }
+  }
+  // ---- P = dY . XW^T over the head's 64 channels; this warp's half of the KW columns
+  const int NT = KW >> 3, nt0 = half * (NT >> 1), ntn = NT >> 1;     // n-tiles [nt0, nt0 + ntn): 4 (KW = 64) or 3 (KW = 48)
+  float accp[2][4][4];
+#pragma unroll
+  for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) accp[mi][nt][e] = 0.f;
+  {
+    const uint32_t a_base = dw_s + lrow * XS_STRIDE + (hl * R + 8 * (lane >> 4)) * 2;
+    const uint32_t b_base = xw_s + ((lane & 7) + 8 * (lane >> 4)) * XS_STRIDE + (hl * R + 8 * ((lane >> 3) & 1)) * 2;
+#pragma unroll
+    for (int kt = 0; kt < R / 16; ++kt) {
+      uint32_t a0[4], a1[4];
+      ldsm_x4(a0, a_base + kt * 32);
+      ldsm_x4(a1, a_base + 16 * XS_STRIDE + kt * 32);
+#pragma unroll
+      for (int jp = 0; jp < 2; ++jp) {
+        if (2 * jp < ntn) {
+          uint32_t bq[4];
+          ldsm_x4(bq, b_base + (nt0 + 2 * jp) * 8 * XS_STRIDE + kt * 32);
+          mma_bf16(accp[0][2 * jp], a0, bq[0], bq[1]);
+          mma_bf16(accp[1][2 * jp], a1, bq[0], bq[1]);
+          if (2 * jp + 1 < ntn) {
+            mma_bf16(accp[0][2 * jp + 1], a0, bq[2], bq[3]);
+            mma_bf16(accp[1][2 * jp + 1], a1, bq[2], bq[3]);
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();                                       // band matrix and windows are no longer read
+  // dw[t][hl][j] = P[t][t + j] * dropout multiplier -> fp32 in the band matrix's place
+  float* dws = reinterpret_cast<float*>(As);
+#pragma unroll
+  for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int row = mi * 16 + (lane >> 2) + 8 * (e >> 1);
+        const int col = (nt0 + nt) * 8 + 2 * (lane & 3) + (e & 1);
+        const int j = col - row;
+        if (nt < ntn && row < TTl && j >= 0 && j < K) {
+          float v = accp[mi][nt][e];
+          if (dr.thr) v = drop_val(dr, ((static_cast<unsigned long long>(t0 + row) * B + b) * p.H + h0 + hl) * K + j, v);
+          dws[(row * HG + hl) * K + j] = v;
+        }
+      }
+  // dx tile -> smem (the x window's place) for coalesced stores
+#pragma unroll
+  for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      const int col = hl * R + chb + nt * 8 + 2 * (lane & 3);
+      const int r0 = mi * 16 + (lane >> 2);
+      *reinterpret_cast<uint32_t*>(xw + r0 * XS_STRIDE + col * 2) = pack_bf16x2(accx[mi][nt][0], accx[mi][nt][1]);
+      *reinterpret_cast<uint32_t*>(xw + (r0 + 8) * XS_STRIDE + col * 2) = pack_bf16x2(accx[mi][nt][2], accx[mi][nt][3]);
+    }
+  __syncthreads();
+  // soft-max backward of the tile's own rows; dlogits overwrite the raw logits in place
+  for (int i = threadIdx.x; i < TTl * HG; i += kThreads) {
+    const int t = i / HG, hq = i - t * HG;
+    bf16* l = lraw + t * HK + hq * K;
+    const float2 st = stat[t * HG + hq];
+    const float* g = dws + (t * HG + hq) * K;
+    float dot = 0.f;
+    for (int j = 0; j < K; ++j) dot = fmaf(__expf(__bfloat162float(l[j]) - st.x) * st.y, g[j], dot);
+    for (int j = 0; j < K; ++j) {
+      const float w = __expf(__bfloat162float(l[j]) - st.x) * st.y;
+      l[j] = __float2bfloat16_rn(w * (g[j] - dot));
+    }
+  }
+  bf16* dxo = reinterpret_cast<bf16*>(p.dx);
+  for (int i = threadIdx.x; i < TTl * nv; i += kThreads) {
+    const int t = i / nv, vc = i - t * nv;
+    *reinterpret_cast<uint4*>(dxo + (static_cast<long>(t0 + t) * B + b) * p.lddx + c0 + vc * 8) =
+        *reinterpret_cast<const uint4*>(xw + t * XS_STRIDE + vc * 16);
+  }
+  __syncthreads();
+  {
+    bf16* dlo = reinterpret_cast<bf16*>(p.dlogits);
+    const int wpr = HK >> 1;
+    for (int i = threadIdx.x; i < TTl * wpr; i += kThreads) {
+      const int t = i / wpr, wd = i - t * wpr;
+      *reinterpret_cast<uint32_t*>(dlo + (static_cast<long>(t0 + t) * B + b) * p.lddl + h0 * K + 2 * wd) =
+          *reinterpret_cast<const uint32_t*>(lraw + t * HK + 2 * wd);
+    }
+  }
+}
 }  // namespace tcv
 
 // ------------------------------------------------------------------------------ single step
@@ -535,6 +725,20 @@ extern "C" int tnt_dynconv_bwd(const tnt_dynconv_bwd_params* p, tnt_stream strea
   dim3 grid(p->B, ngroups, (p->T + kTT - 1) / kTT);
   TNT_CHECK_ARG(p->drop.p >= 0.f && p->drop.p < 1.f, "dynconv_bwd: dropout p = %f", p->drop.p);
   const DropSpec dr = make_drop(p->drop);
+  static const bool tc_on = [] { const char* e = getenv("TNT_DYNCONV_TC"); return !(e && e[0] == '0'); }();
+  if (tc_on && p->dtype == TNT_BF16 && p->C / p->H == tcv::R && p->C % tcv::CC == 0 && p->K <= 33 && p->ldl % 2 == 0 &&
+      p->lddl % 2 == 0 && ((reinterpret_cast<uintptr_t>(p->logits) | reinterpret_cast<uintptr_t>(p->dlogits)) & 3) == 0) {
+    const int KW = (tcv::TT + p->K - 1 + 15) & ~15;
+    const size_t lraw_b = (static_cast<size_t>(KW) * tcv::HG * p->K * 2 + 15) & ~size_t(15);
+    const size_t band_b = std::max<size_t>(static_cast<size_t>(tcv::HG) * tcv::TT * (KW * 2 + 16),
+                                           static_cast<size_t>(tcv::TT) * tcv::HG * p->K * 4);
+    const size_t sm = 2 * static_cast<size_t>(KW) * tcv::XS_STRIDE + band_b + lraw_b + static_cast<size_t>(KW) * tcv::HG * 8;
+    TNT_TRY(set_smem(tcv::dynconv_bwd_tc_kernel, sm));
+    dim3 g2(p->B, p->C / tcv::CC, (p->T + tcv::TT - 1) / tcv::TT);
+    tcv::dynconv_bwd_tc_kernel<<<g2, kThreads, sm, as_stream(stream)>>>(*p, KW, dr);
+    TNT_LAUNCHED();
+    return TNT_OK;
+  }
   if (p->dtype == TNT_BF16) {
     TNT_TRY(set_smem(dynconv_bwd_kernel<bf16>, smem));
     dynconv_bwd_kernel<bf16><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG, dr);
