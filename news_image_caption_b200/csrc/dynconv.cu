@@ -536,6 +536,76 @@ __global__ void __launch_bounds__(kThreads) dynconv_step_kernel(tnt_dynconv_step
   }
 }
 
+// bf16 decode step with every ring read in flight at once: thread = (8-channel vector, one of 4 tap groups); its <= 8
+// ring rows are requested as raw 16-byte loads BEFORE the tap soft-max runs (the version above walks the K-1 rows in a
+// dependent loop on half of its threads: 19 % of the HBM roofline).  K <= 33, C <= 2048.
+constexpr int kStepGroups = 4, kStepTaps = 8;
+__global__ void __launch_bounds__(1024) dynconv_step_fast_kernel(tnt_dynconv_step_params p) {
+  pdl_wait();
+  extern __shared__ float sm[];                          // taps [H][K] fp32, then partial sums [4][C]
+  const int K = p.K, KM = K - 1, R = p.C / p.H, b = blockIdx.x;
+  const int nv = p.C >> 3;
+  const int vc = threadIdx.x % nv, g = threadIdx.x / nv;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  float* part = sm + p.H * K;
+  const int pos = p.pos ? *p.pos : 0;
+  const bf16* ring = reinterpret_cast<const bf16*>(p.ring);
+  uint4 rv[kStepTaps];
+#pragma unroll
+  for (int u = 0; u < kStepTaps; ++u) {
+    const int j = g + kStepGroups * u, s = pos - KM + j;
+    rv[u] = make_uint4(0, 0, 0, 0);
+    if (j < KM && s >= 0) rv[u] = *reinterpret_cast<const uint4*>(ring + (static_cast<long>(s % KM) * p.B + b) * p.C + vc * 8);
+  }
+  uint4 xraw = make_uint4(0, 0, 0, 0);
+  if (g == 0) xraw = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.x) + static_cast<long>(b) * p.ldx + vc * 8);
+  const bf16* lg = reinterpret_cast<const bf16*>(p.logits) + static_cast<long>(b) * p.ldl;
+  for (int h = warp; h < p.H; h += nwarps) warp_softmax_taps(lg + h * K, K, sm + h * K, lane);
+  __syncthreads();
+  const float* w = sm + ((vc * 8) / R) * K;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int u = 0; u < kStepTaps; ++u) {
+    const int j = g + kStepGroups * u;
+    if (j < KM) {
+      const float wj = w[j];
+      const uint32_t q[4] = {rv[u].x, rv[u].y, rv[u].z, rv[u].w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc[2 * i] = fmaf(wj, __uint_as_float(q[i] << 16), acc[2 * i]);
+        acc[2 * i + 1] = fmaf(wj, __uint_as_float(q[i] & 0xffff0000u), acc[2 * i + 1]);
+      }
+    }
+  }
+  if (g == 0) {
+    const float wl = w[K - 1];
+    const uint32_t q[4] = {xraw.x, xraw.y, xraw.z, xraw.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      acc[2 * i] = fmaf(wl, __uint_as_float(q[i] << 16), acc[2 * i]);
+      acc[2 * i + 1] = fmaf(wl, __uint_as_float(q[i] & 0xffff0000u), acc[2 * i + 1]);
+    }
+    if (KM > 0) *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.ring) + (static_cast<long>(pos % KM) * p.B + b) * p.C + vc * 8) = xraw;
+  }
+  float* mine = part + g * p.C + vc * 8;
+  *reinterpret_cast<float4*>(mine) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  *reinterpret_cast<float4*>(mine + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  __syncthreads();
+  if (g == 0) {
+    float o[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = acc[i];
+#pragma unroll
+    for (int gg = 1; gg < kStepGroups; ++gg) {
+      const float4 a0 = *reinterpret_cast<const float4*>(part + gg * p.C + vc * 8);
+      const float4 a1 = *reinterpret_cast<const float4*>(part + gg * p.C + vc * 8 + 4);
+      o[0] += a0.x; o[1] += a0.y; o[2] += a0.z; o[3] += a0.w;
+      o[4] += a1.x; o[5] += a1.y; o[6] += a1.z; o[7] += a1.w;
+    }
+    store8(reinterpret_cast<bf16*>(p.y) + static_cast<long>(b) * p.ldy + vc * 8, o);
+  }
+}
+
 // ------------------------------------------------------------------------------ backward
 // smem: xs [(TT+K-1)][CCP] (inputs t0-(K-1) .. t0+TT-1), dys [(TT+K-1)][CCP] (grads t0 .. t0+TT+K-2),
 //       taps [(TT+K-1)][HG][K] for t0 .. t0+TT+K-2, dws [TT][HG][K]; CCP = CC + 1 (bank spread).
@@ -701,6 +771,16 @@ extern "C" int tnt_dynconv_step(const tnt_dynconv_step_params* p, tnt_stream str
   TNT_TRY(check_common(p->x, p->ldx, 1, p->B, p->C, p->H, p->K, p->dtype));
   TNT_CHECK_ARG(p->logits && p->y && (p->ring || p->K == 1), "dynconv_step: null logits / y / ring");
   const size_t smem = static_cast<size_t>(p->H) * p->K * 4;
+  static const bool fast_on = [] { const char* e = getenv("TNT_DYNCONV_STEP_FAST"); return !(e && e[0] == '0'); }();
+  const int nv = p->C / 8;
+  if (fast_on && p->dtype == TNT_BF16 && p->K <= kStepGroups * kStepTaps + 1 && nv * kStepGroups <= 1024 && (nv * kStepGroups) % 32 == 0 &&
+      (p->H * p->K) % 4 == 0 && p->ldy % 8 == 0 && p->ring) {
+    const size_t sm2 = smem + static_cast<size_t>(kStepGroups) * p->C * 4;
+    TNT_TRY(set_smem(dynconv_step_fast_kernel, sm2));
+    TNT_CUDA(launch_pdl(dynconv_step_fast_kernel, dim3(p->B), dim3(nv * kStepGroups), sm2, as_stream(stream), 1, *p));
+    TNT_LAUNCHED();
+    return TNT_OK;
+  }
   if (p->dtype == TNT_BF16)
     TNT_CUDA(launch_pdl(dynconv_step_kernel<bf16>, dim3(p->B), dim3(kThreads), smem, as_stream(stream), 1, *p));
   else
