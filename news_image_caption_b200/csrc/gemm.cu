@@ -532,7 +532,7 @@ static int dispatch_dtype(const GemmArgs& g, int dt_in, int dt_out, int BN, int 
   return launch_simt<EPI, float, bf16>(g, st);
 }
 
-bool splitk_plan(int M, int N, int K, int* bn_out, int* s_out);                                   // gemm_splitk.cu
+bool splitk_plan(int M, int N, int K, long persistent_tiles, int* bn_out, int* s_out);                                   // gemm_splitk.cu
 int launch_gemm_splitk(const GemmArgs& g, int epi, int dt_out, int BN, int S, cudaStream_t st);
 
 static bool g_force_simt = false;   // test hook: run bf16 problems on the SIMT kernel (cross-check)
@@ -596,7 +596,8 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
   if (use_tc && !g_force_bn && !g.a_mn && !g.b_mn && g.groups == 1 && !g.m_dyn && !n_tiles_out &&
       (epi == EPI_NONE || epi == EPI_RELU || epi == EPI_GLU || epi == EPI_RESIDUAL)) {
     int bn_s, S;
-    if (splitk_plan(g.M, g.N, g.K, &bn_s, &S)) return launch_gemm_splitk(g, epi, p->dtype_out, bn_s, S, st);
+    const long pt = static_cast<long>((g.M + tc::BM * CG - 1) / (tc::BM * CG)) * ((g.N + BN - 1) / BN);
+    if (splitk_plan(g.M, g.N, g.K, pt, &bn_s, &S)) return launch_gemm_splitk(g, epi, p->dtype_out, bn_s, S, st);
   }
   g.n_tiles = (g.N + BN - 1) / BN;
   if (n_tiles_out) *n_tiles_out = g.n_tiles;

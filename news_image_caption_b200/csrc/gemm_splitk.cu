@@ -182,12 +182,15 @@ static int g_split_k = -1;   // test / tuning hook: -1 = automatic, 0 = never, S
 
 // Split factor and tile width for M x N x K, or false when the problem is better served by the persistent kernel:
 // K long enough that the serial k-loop dominates, and few enough tiles that S CTAs per tile still fit one wave.
-bool splitk_plan(int M, int N, int K, int* bn_out, int* s_out) {
+bool splitk_plan(int M, int N, int K, long persistent_tiles, int* bn_out, int* s_out) {
   if (g_split_k == 0) return false;
   const int sms = num_sms();
+  // K = 1024 .. 2047: only S = 2, and only when the persistent kernel would leave at least half of the SMs without a tile
+  // (measured, tools/diag_splitk_k1024.py: 8.1 -> 6.6 us at M=256 N=1024; a loss once the persistent grid is well filled)
+  if (g_split_k < 0 && K < 2048 && persistent_tiles * 2 > sms) return false;
   const int m_tiles = (M + sk::BM - 1) / sk::BM;
   const int num_kb = (K + sk::BK - 1) / sk::BK;
-  const int s_max = g_split_k >= 2 ? g_split_k : std::min(4, K / 1024);
+  const int s_max = g_split_k >= 2 ? g_split_k : (K >= 4096 ? 4 : (K >= 1024 ? 2 : 1));
   for (int S = std::min(s_max, 8); S >= 2; --S) {
     if (num_kb < 2 * S) continue;
     const int bns[3] = {32, 64, 128};

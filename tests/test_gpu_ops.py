@@ -152,7 +152,7 @@ def test_linear_cta_pair(ops, M, N, K):
 
 
 @pytest.mark.parametrize('M,N,K,S', [(256, 1024, 4096, -1), (256, 1024, 2048, -1), (1, 64, 2048, -1), (200, 1000, 4096 + 64, 4),
-                                     (130, 96, 1024, 2), (64, 320, 8192, 8), (300, 40, 3000 + 8, 3)])
+                                     (130, 96, 1024, 2), (64, 320, 8192, 8), (300, 40, 3000 + 8, 3), (256, 1024, 1024, -1), (2048, 112, 1024, -1)])
 def test_linear_split_k(ops, M, N, K, S):
     """The cluster split-K kernel (decode-step GEMMs: few rows, long K) against fp64 and the persistent kernel:
     automatic plan (S = -1) and forced split factors, ragged M / N / K, every epilogue it serves."""
