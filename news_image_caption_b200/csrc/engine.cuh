@@ -86,6 +86,7 @@ struct FwdWs {
   void* kv[TNT_MAX_SOURCES];
   float* lse[TNT_MAX_SOURCES];   // training: attention log-sum-exp [B, H, T] per source (NULL: not saved)
   uint32_t* tile_live[TNT_MAX_SOURCES];   // [B_kv] live 128-key tiles of every context entry (project_kv fills it)
+  int* sched;                    // 2 zeroed ints: dynamic work counters of the decode-step attention (or NULL)
   size_t total;
 };
 // B_kv >= 0: number of context entries the K/V cache holds when it differs from the row batch B (beam search)

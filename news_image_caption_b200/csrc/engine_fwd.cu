@@ -10,7 +10,7 @@ namespace tnt {
 int xattn_check(const tnt_xattn_params* p);
 int xattn_fwd_dispatch(const tnt_xattn_params* p, cudaStream_t st);
 bool xattn_step_supported(const tnt_xattn_params* p);
-int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st);
+int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched = nullptr);
 bool xattn_force_simt();
 
 namespace {
@@ -78,6 +78,7 @@ FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool
   w.CATln = w.CAT;
   for (size_t s = 0; s < ns; ++s)
     w.kv[s] = with_kv ? take(static_cast<size_t>(S[s] + 2) * (B_kv >= 0 ? B_kv : B) * c.n_layers * 2 * d * E) : nullptr;
+  w.sched = with_kv ? static_cast<int*>(take(2 * sizeof(int))) : nullptr;    // work counters of the decode-step attention
   for (size_t s = 0; s < ns; ++s)
     w.tile_live[s] = with_kv ? static_cast<uint32_t*>(take(sizeof(uint32_t) * (B_kv >= 0 ? B_kv : B))) : nullptr;
   w.total = off;
@@ -90,6 +91,7 @@ FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool
 int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st) {
   const tnt_decoder_config& c = D->cfg;
   const int ldkv = c.n_layers * 2 * c.d;
+  if (w.sched) TNT_CUDA(cudaMemsetAsync(w.sched, 0, 2 * sizeof(int), st));   // every launch leaves them at zero again
   for (int s = 0; s < c.n_sources; ++s) {
     const int grid = std::min<long>((static_cast<long>(ctx->B) * ldkv + 255) / 256, 4L * num_sms());
     const bool scan = w.tile_live[s] && ctx->pad_mask[s] && ctx->S[s] > 0;
@@ -192,7 +194,7 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
   }
   if (all_step) {
     const int pid = prof_enabled() ? prof_begin("xattn_step.merged", st) : -1;   // -1 while a graph is being captured
-    TNT_TRY(xattn_fwd_step_multi(aps, ns, st));          // decode step: every source of the layer in one launch
+    TNT_TRY(xattn_fwd_step_multi(aps, ns, st, w.sched));   // decode step: every source of the layer in one launch
     prof_end(pid, st);
   } else {
     for (int s = 0; s < ns; ++s) {
