@@ -280,13 +280,13 @@ typedef struct {
   tnt_dropout drop;   /* dropout on the probabilities (multi_head.py:463), index ((b*H + h)*T + t)*(S + n_extra) + key;
                          the soft-max normaliser (and `lse`) are those of the un-dropped probabilities; `weights`
                          averages the dropped probabilities, as the reference does */
-  const uint32_t* tile_live; /* optional [B] (tnt_xattn_tile_mask): bit i set = keys [128 i, 128 i + 128) of batch row b
+  const uint32_t* tile_live; /* optional [B] (tnt_xattn_tile_mask): bit i (i < 16) set = keys [128 i, 128 i + 128) of batch row b
                          hold at least one un-masked key.  The tcgen05 kernels skip the other tiles entirely (a masked key
                          contributes exactly 0) and walk the rows longest first; NULL = visit every tile */
 } tnt_xattn_params;
 int tnt_xattn_fwd(const tnt_xattn_params* p, tnt_stream stream);
-/* tile bitmask (out [B], S <= 2048) of a key-padding mask [B, >= mask_S] (mask_S = 0: S); keys >= mask_S (the extra rows)
- * are never masked */
+/* out[b] = tile bitmask | live-key count << 16 (S <= 2048) of a key-padding mask [B, >= mask_S] (mask_S = 0: S); keys >=
+ * mask_S (the extra rows) are never masked */
 int tnt_xattn_tile_mask(const uint8_t* mask, int64_t m_stride_b, int B, int S, int mask_S, uint32_t* out, tnt_stream stream);
 
 

@@ -44,6 +44,7 @@ __device__ __forceinline__ uint4 ldg_stream(const void* p) {
 // atomic counter and the last CTA to leave re-zeroes it; captions keep very different numbers of live keys (128..512).
 struct StepBatch {
   tnt_xattn_params p[TNT_MAX_SOURCES];
+  const int* order[TNT_MAX_SOURCES];      // optional per source: caption slots sorted by live keys, longest first
   int n;
   int* sched;
 };
@@ -64,8 +65,10 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(const __grid_co
     item = sm_item;
   }
   if (item >= total) break;
-  const tnt_xattn_params& p = batch.p[item / per_src];
-  const int rem = item % per_src, b = rem / n_hg, hg = rem - b * n_hg;
+  const int src = item / per_src;
+  const tnt_xattn_params& p = batch.p[src];
+  const int rem = item % per_src, slot = rem / n_hg, hg = rem - slot * n_hg;
+  const int b = batch.order[src] ? batch.order[src][slot] : slot;      // long captions are started first (1.7 waves of CTAs)
   const int h = hg * kHeadsPerCta + (lane >> 2), d0 = (lane & 3) * 16;
   const bf16* qp = reinterpret_cast<const bf16*>(p.q) + static_cast<long>(b) * p.q_stride_b + h * 64 + d0;
   const int bk = p.kv_group > 1 ? b / p.kv_group : b;     // beams of one caption share its K / V / mask
@@ -191,7 +194,7 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(const __grid_co
 
 }  // namespace
 
-int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched = nullptr);
+int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched = nullptr, const int* const* orders = nullptr);
 
 bool xattn_step_supported(const tnt_xattn_params* p) {
   if (p->T != 1 || p->dtype != TNT_BF16 || p->D != 64 || (p->H % kHeadsPerCta) != 0 || p->n_extra != 0 || p->weights || p->drop.p > 0.f)
@@ -203,8 +206,29 @@ bool xattn_step_supported(const tnt_xattn_params* p) {
 
 int xattn_fwd_step(const tnt_xattn_params* p, cudaStream_t st) { return xattn_fwd_step_multi(p, 1, st); }
 
+namespace {
+// order[rank] = b, rows ranked by their live-key count (tile_live[b] >> 16, see tile_bits_row), longest first; one CTA
+__global__ void __launch_bounds__(1024) live_order_kernel(const uint32_t* tile_live, int B, int* order) {
+  for (int b = threadIdx.x; b < B; b += 1024) {
+    const uint32_t mine = tile_live[b] >> 16;
+    int rank = 0;
+    for (int o = 0; o < B; ++o) {
+      const uint32_t other = tile_live[o] >> 16;
+      rank += (other > mine) || (other == mine && o < b);
+    }
+    order[rank] = b;
+  }
+}
+}  // namespace
+
+int xattn_live_order(const uint32_t* tile_live, int B, int* order, cudaStream_t st) {
+  live_order_kernel<<<1, 1024, 0, st>>>(tile_live, B, order);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
 // n problems with the same B and H (the sources of one decoder layer), one launch
-int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched) {
+int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched, const int* const* orders) {
   TNT_CHECK_ARG(n >= 1 && n <= TNT_MAX_SOURCES, "xattn_step: %d problems", n);
   StepBatch batch;
   int order[TNT_MAX_SOURCES];
@@ -213,7 +237,10 @@ int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int
     order[i] = i;
   }
   std::sort(order, order + n, [&](int a, int b) { return ps[a].S > ps[b].S; });      // longest source first
-  for (int i = 0; i < n; ++i) batch.p[i] = ps[order[i]];
+  for (int i = 0; i < n; ++i) {
+    batch.p[i] = ps[order[i]];
+    batch.order[i] = (orders && ps[order[i]].kv_group <= 1) ? orders[order[i]] : nullptr;
+  }
   batch.n = n;
   // measured (B = 256, generation bench): pulling items is no faster than one CTA per item (27.7 vs 27.5 ms) -- all 1024 CTAs
   // are co-resident anyway -- so the static mapping stays the default; TNT_STEP_ATTN_DYNAMIC=1 switches the queue on

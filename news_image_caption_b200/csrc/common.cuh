@@ -215,9 +215,10 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
   return r;
 }
 
-// bit i of out[b]: key tile i (128 keys) of batch row b holds at least one key that is not padding.  One warp per row.
+// out[b] = bits | live << 16: bit i (i < 16) = key tile i (128 keys) of batch row b holds at least one key that is not
+// padding; live = number of such keys (saturated at 65535).  One warp per row.
 __device__ __forceinline__ void tile_bits_row(const uint8_t* mask, long m_stride_b, int b, int S, int mask_S, uint32_t* out, int lane) {
-  uint32_t bits = 0;
+  uint32_t bits = 0, live = 0;
   const uint8_t* mrow = mask + static_cast<long>(b) * m_stride_b;
   for (int k0 = 0; k0 < S; k0 += 256) {            // 8 independent byte loads per lane in flight
     bool lv[8];
@@ -227,10 +228,13 @@ __device__ __forceinline__ void tile_bits_row(const uint8_t* mask, long m_stride
       lv[u] = key < S && (key >= mask_S || mrow[key] == 0);
     }
 #pragma unroll
-    for (int u = 0; u < 8; ++u)
-      if (__ballot_sync(0xffffffffu, lv[u])) bits |= 1u << ((k0 + u * 32) / 128);
+    for (int u = 0; u < 8; ++u) {
+      const uint32_t bal = __ballot_sync(0xffffffffu, lv[u]);
+      if (bal) bits |= 1u << ((k0 + u * 32) / 128);
+      live += __popc(bal);
+    }
   }
-  if (lane == 0) out[b] = bits;
+  if (lane == 0) out[b] = (bits & 0xFFFFu) | (min(live, 0xFFFFu) << 16);
 }
 
 }  // namespace tnt

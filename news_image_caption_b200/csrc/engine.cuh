@@ -86,6 +86,7 @@ struct FwdWs {
   void* kv[TNT_MAX_SOURCES];
   float* lse[TNT_MAX_SOURCES];   // training: attention log-sum-exp [B, H, T] per source (NULL: not saved)
   uint32_t* tile_live[TNT_MAX_SOURCES];   // [B_kv] live 128-key tiles of every context entry (project_kv fills it)
+  int* order[TNT_MAX_SOURCES];   // decode engines: context entries sorted by live keys, longest first (or NULL)
   int* sched;                    // 2 zeroed ints: dynamic work counters of the decode-step attention (or NULL)
   size_t total;
 };
@@ -93,7 +94,7 @@ struct FwdWs {
 FwdWs carve_fwd(const tnt_decoder* d, int B, int T, const int* S, void* ws, bool with_kv, int B_kv = -1);
 
 int embed(tnt_decoder* d, const int64_t* ids, int B, int T, void* out, const int* start_pos, cudaStream_t st);
-int project_kv(tnt_decoder* d, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st);
+int project_kv(tnt_decoder* d, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st, bool decode_order = false);
 // one decoder layer on N = T*B rows; `ring`/`pos` != NULL selects the single-step conv (T must be 1)
 int run_layer(tnt_decoder* d, int l, const tnt_contexts* ctx, const FwdWs& w, const void* Xin, void* Xout, int B, int T,
               void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st, int kv_group = 1,

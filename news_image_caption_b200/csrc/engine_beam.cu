@@ -287,7 +287,7 @@ extern "C" int tnt_decoder_generate_beam(tnt_decoder* D, const int64_t* seed, co
   c1.T = 1;
   beam_init_kernel<<<std::min((B * W + 255) / 256, 1024), 256, 0, st>>>(seed, B, W, g.cur, g.bsum, g.ndone, g.pos);
   TNT_LAUNCHED();
-  TNT_TRY(project_kv(D, &c1, g.f, st));
+  TNT_TRY(project_kv(D, &c1, g.f, st, true));
   TNT_TRY(beam_one_step(D, &c1, g, B, W, L, eos, st));                     // step 0 eagerly
   if (L > 1) {
     cudaStream_t cs;

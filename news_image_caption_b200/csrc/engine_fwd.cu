@@ -10,7 +10,8 @@ namespace tnt {
 int xattn_check(const tnt_xattn_params* p);
 int xattn_fwd_dispatch(const tnt_xattn_params* p, cudaStream_t st);
 bool xattn_step_supported(const tnt_xattn_params* p);
-int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched = nullptr);
+int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched = nullptr, const int* const* orders = nullptr);
+int xattn_live_order(const uint32_t* tile_live, int B, int* order, cudaStream_t st);
 bool xattn_force_simt();
 
 namespace {
@@ -79,6 +80,7 @@ FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool
   for (size_t s = 0; s < ns; ++s)
     w.kv[s] = with_kv ? take(static_cast<size_t>(S[s] + 2) * (B_kv >= 0 ? B_kv : B) * c.n_layers * 2 * d * E) : nullptr;
   w.sched = with_kv ? static_cast<int*>(take(2 * sizeof(int))) : nullptr;    // work counters of the decode-step attention
+  for (size_t s = 0; s < ns; ++s) w.order[s] = with_kv ? static_cast<int*>(take(sizeof(int) * (B_kv >= 0 ? B_kv : B))) : nullptr;
   for (size_t s = 0; s < ns; ++s)
     w.tile_live[s] = with_kv ? static_cast<uint32_t*>(take(sizeof(uint32_t) * (B_kv >= 0 ? B_kv : B))) : nullptr;
   w.total = off;
@@ -88,7 +90,7 @@ FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool
 // K/V of every layer for every source in ONE GEMM per source: [S*B, kdim] x [L*2d, kdim]^T (+bias).
 // The reference recomputes these projections in every layer call and every decoding step
 // (multi_head.py:347-352 with incremental_state=None, decoder_flattened.py:305,323); same numbers.
-int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st) {
+int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st, bool decode_order) {
   const tnt_decoder_config& c = D->cfg;
   const int ldkv = c.n_layers * 2 * c.d;
   if (w.sched) TNT_CUDA(cudaMemsetAsync(w.sched, 0, 2 * sizeof(int), st));   // every launch leaves them at zero again
@@ -103,6 +105,8 @@ int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStre
       kv_extra_rows_kernel<float><<<grid + extra, 256, 0, st>>>(static_cast<float*>(w.kv[s]), D->kvrow[s], ctx->S[s], ctx->B, ldkv,
                                                                 grid, ctx->pad_mask[s], w.tile_live[s]);
     TNT_LAUNCHED();
+    // generation: the decode-step attention starts the captions with the most live keys first (once per call)
+    if (decode_order && scan && w.order[s] && ctx->B <= 4096) TNT_TRY(xattn_live_order(w.tile_live[s], ctx->B, w.order[s], st));
     if (ctx->S[s] == 0) continue;
     TNT_CHECK_ARG(ctx->memory[s], "decoder: context '%s' missing", c.source_names[s]);
     char pname[40];
@@ -194,7 +198,10 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
   }
   if (all_step) {
     const int pid = prof_enabled() ? prof_begin("xattn_step.merged", st) : -1;   // -1 while a graph is being captured
-    TNT_TRY(xattn_fwd_step_multi(aps, ns, st, w.sched));   // decode step: every source of the layer in one launch
+    const int* orders[TNT_MAX_SOURCES];
+    for (int s = 0; s < ns; ++s)
+      orders[s] = (aps[s].mask_mode == TNT_MASK_KEY_PADDING && ctx->B <= 4096 && ring) ? w.order[s] : nullptr;
+    TNT_TRY(xattn_fwd_step_multi(aps, ns, st, w.sched, orders));   // decode step: every source of the layer in one launch
     prof_end(pid, st);
   } else {
     for (int s = 0; s < ns; ++s) {

@@ -128,7 +128,7 @@ extern "C" int tnt_decoder_generate(tnt_decoder* D, const int64_t* seed, const t
   c1.T = 1;
   gen_init_kernel<<<1, 1024, 0, st>>>(seed, B, gen_len, eos, g.cur, g.active, ids_out, g.pos);
   TNT_LAUNCHED();
-  TNT_TRY(project_kv(D, &c1, g.f, st));
+  TNT_TRY(project_kv(D, &c1, g.f, st, true));
   TNT_TRY(gen_step(D, &c1, g, B, gen_len, eos, ids_out, logp_out, st));          // step 0 eagerly
   if (gen_len > 1) {
     // steps 1.. : capture ONE step on a private stream (the caller's may be the legacy stream, which

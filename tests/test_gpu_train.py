@@ -110,7 +110,8 @@ def test_xattn_skips_all_padding_key_tiles(ops):
     pad[3, :] = True                       # only the extra keys remain
     pad[4, 5:] = True
     tl = ops.xattn_tile_mask(pad.cuda(), S, S - 2)
-    assert tl.cpu().tolist() == [0b10011, 0b10111, 0b11101, 0b10000, 0b10001, 0b11111]
+    assert [v & 0xFFFF for v in tl.cpu().tolist()] == [0b10011, 0b10111, 0b11101, 0b10000, 0b10001, 0b11111]   # live tiles
+    assert [(v >> 16) & 0xFFFF for v in tl.cpu().tolist()] == [132, 302, 386, 2, 7, 514]                        # live keys
     scale = D ** -0.5
     lse0 = torch.empty(B, H, T, device='cuda')
     lse1 = torch.empty(B, H, T, device='cuda')
