@@ -378,7 +378,9 @@ size_t tnt_decoder_workspace_bytes(const tnt_decoder* d, int B, int T, const int
 /* workspace of tnt_decoder_nll / tnt_decoder_log_prob for n_rows rows */
 size_t tnt_decoder_loss_workspace_bytes(const tnt_decoder* d, int n_rows);
 
-/* teacher-forced forward.  ids [B,T] -> X [B,T,d] (engine dtype); attn optional [B,T,S_article+2] fp32 */
+/* teacher-forced forward.  ids [B,T] -> X [B,T,d] (engine dtype); attn optional [B,T,S_w+2] fp32: the head-averaged
+ * attention of the last layer over source w = the one the reference's layer returns -- "entity" when the decoder has
+ * such a source (decoder_entity_pointer.py:326-334 overwrites attn last), else "article" (decoder_flattened.py:325) */
 int tnt_decoder_forward(tnt_decoder* d, const int64_t* ids, const tnt_contexts* ctx, void* X_out,
                         float* attn_out, void* workspace, size_t workspace_bytes, tnt_stream stream);
 /* AdaptiveLoss(reduction='sum'): out[0] = loss sum (nats), out[1] = number of non-pad targets */
@@ -419,11 +421,33 @@ typedef struct {
   float* logprob; int64_t ldp;             /* [B*T, V] fp32, in / out */
   float* p_gen;                            /* optional [B*T] */
   int B, T, S, d, V, dtype;
+  int64_t* best_tok; float* best_logp;     /* optional [B*T]: arg-max / max of the mixed row (greedy generation) */
 } tnt_pointer_params;
+/* inp_embed == NULL selects the entity-pointer head (transformer_entity_pointer.py:198-210): x is then the hidden
+ * relu(project_first_p_gens(cat(inp_embed, X))) [B*T, d] and p_gen = sigmoid(w_pgen[:d] . x + b_pgen); `attn` /
+ * `article_ids` are the ENTITY attention and the entity token ids. */
 int tnt_pointer_mix(const tnt_pointer_params* p, tnt_stream stream);
 /* F.nll_loss(logprob, target, ignore_index = pad, reduction = 'sum') (transformer_context_pointer.py:128):
  * out2 = [sum, number of counted rows] */
 int tnt_nll_rows(const float* logprob, int64_t ldp, const int64_t* target, int rows, int pad, float* out2, tnt_stream stream);
+
+/* Copy head used inside the generation loop (tnt_decoder_generate_pointer).  Plain pointer head
+ * (decoder_pointer.py:138-141): w_hidden == NULL, w_pgen [2d].  Entity-pointer head (transformer_entity_pointer.py:
+ * 78-79,198-200): w_hidden = weight-norm-folded project_first_p_gens weight [d_hidden, 2d] in the engine dtype,
+ * b_hidden [d_hidden] fp32, w_pgen [d_hidden].  copy_ids [B, S_copy] are the token ids of the positions of the source
+ * whose attention is copied (the article, or the entity source when the decoder has one). */
+typedef struct {
+  const float* w_pgen; float b_pgen;
+  const void* w_hidden; const float* b_hidden; int d_hidden;
+  const int64_t* copy_ids; int S_copy;
+} tnt_pointer_head;
+/* Greedy generation through the copy head -- the `_generate` loop of the pointer models with sampling_topk = 1
+ * (transformer_entity_pointer.py:375-470): per step the decoder layers (incremental), the full-vocabulary
+ * log-probabilities, the copy mix and the arg-max of the mixed row.  Outputs as tnt_decoder_generate. */
+size_t tnt_decoder_generate_pointer_workspace_bytes(const tnt_decoder* d, int B, int gen_len, const int* S, int d_hidden);
+int tnt_decoder_generate_pointer(tnt_decoder* d, const int64_t* seed, const tnt_contexts* ctx, const tnt_pointer_head* head,
+                                 int gen_len, int eos, int64_t* ids_out, float* logp_out, int* steps_host,
+                                 void* workspace, size_t workspace_bytes, tnt_stream stream);
 
 size_t tnt_decoder_generate_workspace_bytes(const tnt_decoder* d, int B, int gen_len, const int* S);
 int tnt_decoder_generate(tnt_decoder* d, const int64_t* seed, const tnt_contexts* ctx, int gen_len, int eos,

@@ -3,7 +3,8 @@ harsh157/news_image_caption: hand-written CUDA kernels behind a C ABI (include/t
 host-side mirror of the reference's decoder / loss module interface.  No CPU fallback."""
 from . import _lib  # noqa: F401
 from ._lib import TntError, lib, require_device  # noqa: F401
-from .decoder import AdaptiveLoss, DynamicConvDecoder, DynamicConvDecoderPointer  # noqa: F401
+from .decoder import (AdaptiveLoss, DynamicConvDecoder, DynamicConvDecoderEntityPointer,  # noqa: F401
+                      DynamicConvDecoderPointer)
 from . import modules, transformer_v2  # noqa: F401  (module-level mirrors; nothing runs at import)
 
-__all__ = ['DynamicConvDecoder', 'DynamicConvDecoderPointer', 'AdaptiveLoss', 'lib', 'require_device', 'TntError']
+__all__ = ['DynamicConvDecoder', 'DynamicConvDecoderPointer', 'DynamicConvDecoderEntityPointer', 'AdaptiveLoss', 'lib', 'require_device', 'TntError']

@@ -41,7 +41,12 @@ def drop_site(layer, kind):
 class PointerParams(C.Structure):
     _fields_ = [('x', vp), ('ldx', i64), ('inp_embed', vp), ('lde', i64), ('w_pgen', vp), ('b_pgen', f32), ('attn', vp),
                 ('attn_ld', i64), ('article_ids', vp), ('logprob', vp), ('ldp', i64), ('p_gen', vp), ('B', i32), ('T', i32),
-                ('S', i32), ('d', i32), ('V', i32), ('dtype', i32)]
+                ('S', i32), ('d', i32), ('V', i32), ('dtype', i32), ('best_tok', vp), ('best_logp', vp)]
+
+
+class PointerHead(C.Structure):
+    _fields_ = [('w_pgen', vp), ('b_pgen', f32), ('w_hidden', vp), ('b_hidden', vp), ('d_hidden', i32), ('copy_ids', vp),
+                ('S_copy', i32)]
 
 
 class LinearParams(C.Structure):
@@ -174,6 +179,9 @@ _SIGS = {
     'tnt_pointer_mix': (i32, [C.POINTER(PointerParams), vp]),
     'tnt_nll_rows': (i32, [vp, i64, vp, i32, i32, vp, vp]),
     'tnt_decoder_generate_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
+    'tnt_decoder_generate_pointer_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32), i32]),
+    'tnt_decoder_generate_pointer': (i32, [vp, vp, C.POINTER(Contexts), C.POINTER(PointerHead), i32, i32, vp, vp,
+                                           C.POINTER(i32), vp, C.c_size_t, vp]),
     'tnt_decoder_generate': (i32, [vp, vp, C.POINTER(Contexts), i32, i32, vp, vp, C.POINTER(i32), vp, C.c_size_t, vp]),
     'tnt_decoder_beam_workspace_bytes': (C.c_size_t, [vp, i32, i32, i32, C.POINTER(i32)]),
     'tnt_decoder_generate_beam': (i32, [vp, vp, C.POINTER(Contexts), i32, i32, i32, vp, vp, vp, vp, C.c_size_t, vp]),

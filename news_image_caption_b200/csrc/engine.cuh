@@ -57,7 +57,7 @@ struct tnt_decoder {
   int emb_dim[TNT_MAX_CLUSTERS] = {};
   std::vector<cudaEvent_t> stage_events;   // training: gradients of stage i are final (tnt_decoder_stream_wait_stage)
   std::map<std::string, float*> grads; // training: fp32 gradient buffer per state_dict key (tnt_decoder_set_grad)
-  int article_idx = -1;
+  int article_idx = -1;   // source whose head-averaged attention the forward returns ("entity" if present, else "article")
   tnt_dropout_config drop_cfg = {};    // training dropout (tnt_decoder_set_dropout); all zero = off
   uint64_t drop_step = 0;              // training steps issued since the configuration was set
   // pipelined host scoring (tnt_decoder_score_host_submit / _wait): copy stream + per-slot events

@@ -100,10 +100,156 @@ int gen_step(tnt_decoder* D, const tnt_contexts* ctx1, const GenWs& g, int B, in
   TNT_LAUNCHED();
   return TNT_OK;
 }
+
+// ---- generation through the copy head (pointer / entity-pointer models)
+struct PtrWs {
+  GenWs g;
+  void* cat;       // [B, 2d]  cat(inp_embed, X) of the step: decoder_pointer.py:139 / decoder_entity_pointer.py:144
+  void* hid;       // [B, d_hidden] relu(project_first_p_gens(cat))  (entity-pointer head)
+  float* attn;     // [B, S_w + 2] head-averaged attention of the last layer over the copied source
+  float* lp;       // [B, V] full-vocabulary log-probabilities, mixed in place
+  void* ada; size_t ada_bytes, total;
+};
+
+PtrWs carve_ptr(const tnt_decoder* D, int B, const int* S, int d_hidden, void* ws) {
+  PtrWs w;
+  w.g = carve_gen(D, B, S, ws);
+  size_t off = w.g.total;
+  auto take = [&](size_t bytes) {
+    void* p = ws ? static_cast<char*>(ws) + off : nullptr;
+    off += al256(bytes);
+    return p;
+  };
+  const int sw = D->article_idx >= 0 ? S[D->article_idx] : 0;
+  w.cat = take(static_cast<size_t>(B) * 2 * D->cfg.d * D->esz());
+  w.hid = take(static_cast<size_t>(B) * std::max(d_hidden, 8) * D->esz());
+  w.attn = static_cast<float*>(take(sizeof(float) * B * (sw + 2)));
+  w.lp = static_cast<float*>(take(sizeof(float) * static_cast<size_t>(B) * D->cfg.vocab));
+  w.ada_bytes = adasoftmax_workspace_bytes(D->ada, B, true);
+  w.ada = take(w.ada_bytes);
+  w.total = off;
+  return w;
+}
+
+int gen_step_pointer(tnt_decoder* D, const tnt_contexts* ctx1, const PtrWs& w, const tnt_pointer_head* hd, int B, int L,
+                     int eos, int64_t* ids_out, float* logp_out, cudaStream_t st) {
+  const GenWs& g = w.g;
+  const int d = D->cfg.d, dt = D->cfg.dtype;
+  const size_t E = D->esz();
+  tnt_embed_params e = {};
+  e.ids = g.cur; e.table = D->table; e.pos_table = D->pos_table; e.out = g.f.X0; e.ldo = d; e.start_pos = g.pos;
+  e.B = B; e.T = 1; e.d = d; e.n_pos = D->cfg.max_positions; e.pad_idx = D->cfg.pad_idx; e.dtype = dt;
+  TNT_TRY(tnt_embed_fwd(&e, st));
+  // inp_embed is kept as the left half of `cat` (the layers overwrite X0)
+  TNT_CUDA(cudaMemcpy2DAsync(w.cat, 2 * d * E, g.f.X0, d * E, d * E, B, cudaMemcpyDeviceToDevice, st));
+  const int Ls = D->cfg.n_layers;
+  for (int l = 0; l < Ls; ++l)
+    TNT_TRY(run_layer(D, l, ctx1, g.f, g.f.X0, g.f.X0, B, 1, g.ring[l], g.pos, l == Ls - 1 ? w.attn : nullptr, false, st));
+  TNT_TRY(adasoftmax_logprob(D->ada, g.f.X0, d, B, w.lp, w.ada, w.ada_bytes, st));
+  tnt_pointer_params pp = {};
+  pp.w_pgen = hd->w_pgen; pp.b_pgen = hd->b_pgen;
+  if (hd->w_hidden) {
+    TNT_CUDA(cudaMemcpy2DAsync(static_cast<char*>(w.cat) + d * E, 2 * d * E, g.f.X0, d * E, d * E, B, cudaMemcpyDeviceToDevice, st));
+    tnt_linear_params lp = {};
+    lp.a = w.cat; lp.lda = 2 * d; lp.w = hd->w_hidden; lp.ldw = 2 * d; lp.bias = hd->b_hidden; lp.c = w.hid; lp.ldc = hd->d_hidden;
+    lp.M = B; lp.N = hd->d_hidden; lp.K = 2 * d; lp.groups = 1; lp.dtype_in = dt; lp.dtype_out = dt; lp.epilogue = TNT_EPI_RELU;
+    lp.alpha = 1.f;
+    TNT_TRY(tnt_linear_fwd(&lp, st));
+    pp.x = w.hid; pp.ldx = hd->d_hidden; pp.inp_embed = nullptr; pp.d = hd->d_hidden;
+  } else {
+    pp.x = g.f.X0; pp.ldx = d; pp.inp_embed = w.cat; pp.lde = 2 * d; pp.d = d;
+  }
+  pp.attn = w.attn; pp.attn_ld = hd->S_copy + 2; pp.article_ids = hd->copy_ids;
+  pp.logprob = w.lp; pp.ldp = D->cfg.vocab;
+  pp.B = B; pp.T = 1; pp.S = hd->S_copy; pp.V = D->cfg.vocab; pp.dtype = dt;
+  pp.best_tok = g.tok; pp.best_logp = g.logp;
+  TNT_TRY(tnt_pointer_mix(&pp, st));
+  gen_update_kernel<<<1, 1024, 0, st>>>(g.tok, g.logp, B, L, eos, D->cfg.pad_idx, g.cur, g.active, ids_out, logp_out, g.pos);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+// step 0 eagerly, steps 1.. replayed from ONE captured CUDA graph (the step counter lives on the device)
+template <typename Step>
+int run_steps(int gen_len, cudaStream_t st, Step&& step) {
+  TNT_TRY(step(st));
+  if (gen_len <= 1) return TNT_OK;
+  // capture on a private stream (the caller's may be the legacy stream, which cannot be captured)
+  cudaStream_t cs;
+  TNT_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  int rc = TNT_OK;
+  cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
+  const uint64_t n0 = tnt_launch_count();
+  if (e == cudaSuccess) {
+    rc = step(cs);
+    e = cudaStreamEndCapture(cs, &graph);
+  }
+  const int per_step = static_cast<int>(tnt_launch_count() - n0);   // kernels recorded in the graph
+  if (rc == TNT_OK && e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
+  if (rc == TNT_OK && e == cudaSuccess) {
+    for (int i = 1; i < gen_len && e == cudaSuccess; ++i) e = cudaGraphLaunch(exec, st);
+    count_launch((gen_len - 2) * per_step);   // capture counted one step; gen_len-1 replays executed
+  }
+  if (exec) cudaGraphExecDestroy(exec);
+  if (graph) cudaGraphDestroy(graph);
+  cudaStreamDestroy(cs);
+  if (rc != TNT_OK) return rc;
+  if (e != cudaSuccess) {
+    set_error("decoder_generate: CUDA graph replay failed: %s", cudaGetErrorString(e));
+    return TNT_ERR_CUDA;
+  }
+  return TNT_OK;
+}
 }  // namespace
 }  // namespace tnt
 
 using namespace tnt;
+
+extern "C" size_t tnt_decoder_generate_pointer_workspace_bytes(const tnt_decoder* d, int B, int gen_len, const int* S,
+                                                               int d_hidden) {
+  (void)gen_len;
+  if (!d || !S) return 0;
+  return carve_ptr(d, B, S, d_hidden, nullptr).total;
+}
+
+extern "C" int tnt_decoder_generate_pointer(tnt_decoder* D, const int64_t* seed, const tnt_contexts* ctx,
+                                            const tnt_pointer_head* head, int gen_len, int eos, int64_t* ids_out,
+                                            float* logp_out, int* steps_host, void* workspace, size_t workspace_bytes,
+                                            tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized, "decoder_generate_pointer: decoder not finalized");
+  TNT_CHECK_ARG(seed && ctx && head && ids_out && logp_out && workspace && gen_len > 0, "decoder_generate_pointer: bad arguments");
+  TNT_CHECK_ARG(head->w_pgen && head->copy_ids, "decoder_generate_pointer: head weights / copy ids missing");
+  TNT_CHECK_ARG(D->article_idx >= 0, "decoder_generate_pointer: the decoder has no article / entity source to copy from");
+  TNT_CHECK_ARG(head->S_copy == ctx->S[D->article_idx], "decoder_generate_pointer: copy_ids cover %d positions, source '%s' has %d",
+                head->S_copy, D->cfg.source_names[D->article_idx], ctx->S[D->article_idx]);
+  TNT_CHECK_ARG(!head->w_hidden || (head->b_hidden && head->d_hidden > 0 && head->d_hidden % 8 == 0),
+                "decoder_generate_pointer: hidden layer of the entity-pointer head");
+  const int B = ctx->B;
+  TNT_CHECK_ARG(gen_len + D->cfg.pad_idx + 1 <= D->cfg.max_positions, "decoder_generate_pointer: gen_len exceeds the position table");
+  PtrWs w = carve_ptr(D, B, ctx->S, head->w_hidden ? head->d_hidden : 0, workspace);
+  if (w.total > workspace_bytes) {
+    set_error("decoder_generate_pointer: workspace %zu < %zu", workspace_bytes, w.total);
+    return TNT_ERR_WORKSPACE;
+  }
+  cudaStream_t st = as_stream(stream);
+  tnt_contexts c1 = *ctx;
+  c1.T = 1;
+  gen_init_kernel<<<1, 1024, 0, st>>>(seed, B, gen_len, eos, w.g.cur, w.g.active, ids_out, w.g.pos);
+  TNT_LAUNCHED();
+  TNT_TRY(project_kv(D, &c1, w.g.f, st, true));
+  TNT_TRY(run_steps(gen_len, st, [&](cudaStream_t s) {
+    return gen_step_pointer(D, &c1, w, head, B, gen_len, eos, ids_out, logp_out, s);
+  }));
+  if (steps_host) {
+    int two[2];
+    TNT_CUDA(cudaMemcpyAsync(two, w.g.pos, sizeof(two), cudaMemcpyDeviceToHost, st));
+    TNT_CUDA(cudaStreamSynchronize(st));
+    *steps_host = two[1] < 0 ? gen_len : two[1];
+  }
+  return TNT_OK;
+}
 
 extern "C" size_t tnt_decoder_generate_workspace_bytes(const tnt_decoder* d, int B, int gen_len, const int* S) {
   (void)gen_len;
@@ -129,36 +275,7 @@ extern "C" int tnt_decoder_generate(tnt_decoder* D, const int64_t* seed, const t
   gen_init_kernel<<<1, 1024, 0, st>>>(seed, B, gen_len, eos, g.cur, g.active, ids_out, g.pos);
   TNT_LAUNCHED();
   TNT_TRY(project_kv(D, &c1, g.f, st, true));
-  TNT_TRY(gen_step(D, &c1, g, B, gen_len, eos, ids_out, logp_out, st));          // step 0 eagerly
-  if (gen_len > 1) {
-    // steps 1.. : capture ONE step on a private stream (the caller's may be the legacy stream, which
-    // cannot be captured) and replay it on the caller's stream.
-    cudaStream_t cs;
-    TNT_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
-    cudaGraph_t graph = nullptr;
-    cudaGraphExec_t exec = nullptr;
-    int rc = TNT_OK;
-    cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
-    const uint64_t n0 = tnt_launch_count();
-    if (e == cudaSuccess) {
-      rc = gen_step(D, &c1, g, B, gen_len, eos, ids_out, logp_out, cs);
-      e = cudaStreamEndCapture(cs, &graph);
-    }
-    const int per_step = static_cast<int>(tnt_launch_count() - n0);   // kernels recorded in the graph
-    if (rc == TNT_OK && e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
-    if (rc == TNT_OK && e == cudaSuccess) {
-      for (int i = 1; i < gen_len && e == cudaSuccess; ++i) e = cudaGraphLaunch(exec, st);
-      count_launch((gen_len - 2) * per_step);   // capture counted one step; gen_len-1 replays executed
-    }
-    if (exec) cudaGraphExecDestroy(exec);
-    if (graph) cudaGraphDestroy(graph);
-    cudaStreamDestroy(cs);
-    if (rc != TNT_OK) return rc;
-    if (e != cudaSuccess) {
-      set_error("decoder_generate: CUDA graph replay failed: %s", cudaGetErrorString(e));
-      return TNT_ERR_CUDA;
-    }
-  }
+  TNT_TRY(run_steps(gen_len, st, [&](cudaStream_t s) { return gen_step(D, &c1, g, B, gen_len, eos, ids_out, logp_out, s); }));
   if (steps_host) {
     int two[2];
     TNT_CUDA(cudaMemcpyAsync(two, g.pos, sizeof(two), cudaMemcpyDeviceToHost, st));

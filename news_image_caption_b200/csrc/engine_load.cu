@@ -165,7 +165,9 @@ extern "C" tnt_decoder* tnt_decoder_create(const tnt_decoder_config* cfg) {
   tnt_decoder* D = new tnt_decoder();
   D->cfg = *cfg;
   for (int s = 0; s < cfg->n_sources; ++s)
-    if (!strcmp(cfg->source_names[s], "article")) D->article_idx = s;
+    if (!strcmp(cfg->source_names[s], "article") && D->article_idx < 0) D->article_idx = s;
+  for (int s = 0; s < cfg->n_sources; ++s)      // the entity-pointer layer returns the ENTITY attention (decoder_entity_pointer.py:326-334)
+    if (!strcmp(cfg->source_names[s], "entity")) D->article_idx = s;
   D->wbytes = plan(D, nullptr);
   return D;
 }

@@ -30,14 +30,21 @@ template <typename T>
 __global__ void __launch_bounds__(kThreads) pointer_mix_kernel(tnt_pointer_params p, int use_smem) {
   extern __shared__ float sm[];
   __shared__ float red[kThreads / 32];
+  __shared__ int red_i[kThreads / 32];
   __shared__ float s_pgen;
   const int row = blockIdx.x, b = row / p.T, t = row - b * p.T;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   // ---- p_gen = sigmoid(w[:d] . inp_embed[t, b] + w[d:] . X[b, t] + bias)
   {
-    const T* e = reinterpret_cast<const T*>(p.inp_embed) + (static_cast<long>(t) * p.B + b) * p.lde;
+    //      (entity-pointer head, inp_embed == nullptr: x is the hidden layer and p_gen = sigmoid(w . x + bias))
     const T* x = reinterpret_cast<const T*>(p.x) + static_cast<long>(row) * p.ldx;
-    float s = dot_row(e, p.w_pgen, p.d, tid, kThreads) + dot_row(x, p.w_pgen + p.d, p.d, tid, kThreads);
+    float s;
+    if (p.inp_embed) {
+      const T* e = reinterpret_cast<const T*>(p.inp_embed) + (static_cast<long>(t) * p.B + b) * p.lde;
+      s = dot_row(e, p.w_pgen, p.d, tid, kThreads) + dot_row(x, p.w_pgen + p.d, p.d, tid, kThreads);
+    } else {
+      s = dot_row(x, p.w_pgen, p.d, tid, kThreads);
+    }
     s = warp_sum(s);
     if (lane == 0) red[warp] = s;
     __syncthreads();
@@ -65,7 +72,38 @@ __global__ void __launch_bounds__(kThreads) pointer_mix_kernel(tnt_pointer_param
     if (id >= 0 && id < p.V) atomicAdd(buf + id, (1.f - pg) * at[s]);
   }
   __syncthreads();
-  for (int v = tid; v < p.V; v += kThreads) lp[v] = __logf(fminf(fmaxf(buf[v], 1e-10f), 1.f));
+  float best = -INFINITY;
+  int best_v = 0x7fffffff;
+  for (int v = tid; v < p.V; v += kThreads) {
+    const float l = __logf(fminf(fmaxf(buf[v], 1e-10f), 1.f));
+    lp[v] = l;
+    if (l > best) { best = l; best_v = v; }       // ascending v per thread: the first maximum is kept
+  }
+  if (p.best_tok) {                                // arg-max of the mixed row, lowest index on ties
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int ov = __shfl_xor_sync(0xffffffffu, best_v, o);
+      if (ob > best || (ob == best && ov < best_v)) { best = ob; best_v = ov; }
+    }
+    __syncthreads();
+    if (lane == 0) { red[warp] = best; red_i[warp] = best_v; }
+    __syncthreads();
+    if (warp == 0) {
+      best = lane < kThreads / 32 ? red[lane] : -INFINITY;
+      best_v = lane < kThreads / 32 ? red_i[lane] : 0x7fffffff;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int ov = __shfl_xor_sync(0xffffffffu, best_v, o);
+        if (ob > best || (ob == best && ov < best_v)) { best = ob; best_v = ov; }
+      }
+      if (lane == 0) {
+        p.best_tok[row] = best_v;
+        if (p.best_logp) p.best_logp[row] = best;
+      }
+    }
+  }
 }
 
 // out2 += [sum of -lp[row, target[row]] over rows with target != pad, number of such rows]
@@ -92,11 +130,11 @@ __global__ void __launch_bounds__(256) nll_rows_kernel(const float* lp, long ldp
 
 extern "C" int tnt_pointer_mix(const tnt_pointer_params* p, tnt_stream stream) {
   using namespace tnt;
-  TNT_CHECK_ARG(p && p->x && p->inp_embed && p->w_pgen && p->attn && p->article_ids && p->logprob, "pointer_mix: null pointer");
+  TNT_CHECK_ARG(p && p->x && p->w_pgen && p->attn && p->article_ids && p->logprob, "pointer_mix: null pointer");
   TNT_CHECK_ARG(p->B > 0 && p->T > 0 && p->S >= 0 && p->V > 0 && p->d > 0 && p->d % 8 == 0, "pointer_mix: bad shape");
   TNT_CHECK_ARG(p->attn_ld >= p->S && p->ldp >= p->V, "pointer_mix: leading dimensions");
   TNT_CHECK_ARG(p->dtype == TNT_F32 || p->dtype == TNT_BF16, "pointer_mix: dtype");
-  TNT_CHECK_ALIGN(aligned16(p->x) && aligned16(p->inp_embed) && p->ldx % 8 == 0 && p->lde % 8 == 0, "pointer_mix: x / inp_embed alignment");
+  TNT_CHECK_ALIGN(aligned16(p->x) && aligned16(p->inp_embed) && p->ldx % 8 == 0 && (!p->inp_embed || p->lde % 8 == 0), "pointer_mix: x / inp_embed alignment");
   const size_t row_bytes = static_cast<size_t>(p->V) * sizeof(float);
   const int use_smem = row_bytes <= 220 * 1024;
   const size_t smem = use_smem ? row_bytes : 0;

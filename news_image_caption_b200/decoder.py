@@ -15,8 +15,9 @@ import torch.nn as nn
 from . import _lib
 from ._lib import TNT_BF16, TNT_F32
 
-SOURCE_ORDER = ('image', 'article', 'faces', 'obj')          # concat order, decoder_faces_objects.py:296-383
-DEFAULT_SOURCE_DIM = {'image': 2048, 'article': 1024, 'faces': 512, 'obj': 2048}
+# concat order: decoder_faces_objects.py:296-383 (image, article, faces, obj), decoder_entity_pointer.py:287-340 (image, article, entity)
+SOURCE_ORDER = ('image', 'article', 'entity', 'faces', 'obj')
+DEFAULT_SOURCE_DIM = {'image': 2048, 'article': 1024, 'entity': 1024, 'faces': 512, 'obj': 2048}
 
 
 def _ptr(t):
@@ -484,30 +485,44 @@ class DynamicConvDecoderPointer(DynamicConvDecoder):
         _register(self, 'project_p_gens.weight_g', torch.ones(1, 1, device=dev))
         _register(self, 'project_p_gens.weight_v', torch.zeros(1, 2 * self.d, device=dev))
 
-    def forward(self, prev_target, contexts, article_ids, incremental_state=None, need_attn=True):
+    def _embed(self, ids):
+        B, T = ids.shape
+        emb = torch.empty(T * B, self.d, dtype=self.torch_dtype, device='cuda')
+        _lib.check(_lib.lib().tnt_decoder_embed(self._h(), _ptr(ids), B, T, _ptr(emb), _stream()), 'tnt_decoder_embed')
+        return emb
+
+    def _p_gen_inputs(self, X, emb, B, T):
+        """-> (x, ldx, inp_embed | None, lde, w_pgen fp32, bias, d, keep-alive list) of tnt_pointer_params."""
         from . import ops
+        pg = self.project_p_gens
+        w = ops.wn_fold(pg.weight_v.detach(), pg.weight_g.detach()).view(-1).contiguous()     # g * v / ||v||, fp32 [2d]
+        return X, self.d, emb, self.d, w, float(pg.bias.item()), self.d, [w]
+
+    def _mix(self, X, emb, attn, copy_ids, B, T):
+        """decoder_pointer.py:151-216 output_layer, in place on the full-vocabulary log-probabilities."""
+        L = _lib.lib()
+        lp = self.get_normalized_probs((X, None), log_probs=True)                 # [B, T, V] fp32
+        ids = copy_ids.to('cuda', torch.long).contiguous()
+        if tuple(ids.shape) != (B, attn.shape[2] - 2):
+            raise ValueError('the copied token ids must be [B, S] of the attended source (S = %d)' % (attn.shape[2] - 2))
+        x, ldx, e, lde, w, bias, d, keep = self._p_gen_inputs(X, emb, B, T)
+        p = _lib.PointerParams()
+        p.x, p.ldx, p.inp_embed, p.lde = x.data_ptr(), ldx, (e.data_ptr() if e is not None else None), lde
+        p.w_pgen, p.b_pgen = w.data_ptr(), bias
+        p.attn, p.attn_ld, p.article_ids = attn.data_ptr(), attn.shape[2], ids.data_ptr()
+        p_gen = torch.empty(B, T, 1, dtype=torch.float32, device='cuda')
+        p.logprob, p.ldp, p.p_gen = lp.data_ptr(), self.vocab, p_gen.data_ptr()
+        p.B, p.T, p.S, p.d, p.V, p.dtype = B, T, ids.shape[1], d, self.vocab, self.dtype_code
+        _lib.check(L.tnt_pointer_mix(C.byref(p), _stream()), 'tnt_pointer_mix')
+        return lp, p_gen
+
+    def forward(self, prev_target, contexts, article_ids, incremental_state=None, need_attn=True):
         X, extra = super().forward(prev_target, contexts, incremental_state, need_attn=True)
         ids = prev_target['roberta'] if isinstance(prev_target, dict) else prev_target
         ids = ids.to('cuda', torch.long).contiguous()
         B, T = ids.shape
-        L, h = _lib.lib(), self._h()
-        emb = torch.empty(T * B, self.d, dtype=self.torch_dtype, device='cuda')
-        _lib.check(L.tnt_decoder_embed(h, _ptr(ids), B, T, _ptr(emb), _stream()), 'tnt_decoder_embed')
-        lp = self.get_normalized_probs((X, None), log_probs=True)                 # [B, T, V] fp32
-        pg = self.project_p_gens
-        w = ops.wn_fold(pg.weight_v.detach(), pg.weight_g.detach()).view(-1).contiguous()     # g * v / ||v||, fp32 [2d]
-        art = article_ids.to('cuda', torch.long).contiguous()
         attn = extra['attn']
-        p = _lib.PointerParams()
-        p.x, p.ldx, p.inp_embed, p.lde = X.data_ptr(), self.d, emb.data_ptr(), self.d
-        p.w_pgen, p.b_pgen = w.data_ptr(), float(pg.bias.item())
-        p.attn, p.attn_ld, p.article_ids = attn.data_ptr(), attn.shape[2], art.data_ptr()
-        p_gen = torch.empty(B, T, 1, dtype=torch.float32, device='cuda')
-        p.logprob, p.ldp, p.p_gen = lp.data_ptr(), self.vocab, p_gen.data_ptr()
-        p.B, p.T, p.S, p.d, p.V, p.dtype = B, T, art.shape[1], self.d, self.vocab, self.dtype_code
-        if art.shape != (B, attn.shape[2] - 2):
-            raise ValueError('article_ids must be [B, S_article]')
-        _lib.check(L.tnt_pointer_mix(C.byref(p), _stream()), 'tnt_pointer_mix')
+        lp, p_gen = self._mix(X, self._embed(ids), attn, article_ids, B, T)
         return lp, {'attn': attn, 'p_gens': p_gen, 'inner_states': None}
 
     def nll(self, lprobs, target):
@@ -521,12 +536,99 @@ class DynamicConvDecoderPointer(DynamicConvDecoder):
         return out
 
     def train_step(self, *a, **k):
-        raise NotImplementedError('DynamicConvDecoderPointer: the copy head is implemented for inference / scoring only')
+        raise NotImplementedError('%s: the copy head is implemented for inference / scoring / generation only'
+                                  % type(self).__name__)
 
-    def generate(self, *a, **k):
-        raise NotImplementedError('DynamicConvDecoderPointer: generation through the copy head is not implemented')
+    def _head(self, copy_ids):
+        """-> (tnt_pointer_head, keep-alive list) for the generation loop."""
+        from . import ops
+        pg = self.project_p_gens
+        w = ops.wn_fold(pg.weight_v.detach(), pg.weight_g.detach()).view(-1).contiguous()
+        hd = _lib.PointerHead()
+        hd.w_pgen, hd.b_pgen = w.data_ptr(), float(pg.bias.item())
+        hd.w_hidden, hd.b_hidden, hd.d_hidden = None, None, 0
+        hd.copy_ids, hd.S_copy = copy_ids.data_ptr(), copy_ids.shape[1]
+        return hd, [w]
 
-    generate_beam = generate
+    def generate(self, seed, contexts, copy_ids, gen_len=100, eos=2, trim=True):
+        """Greedy `_generate` of the pointer models (sampling_topk = 1; transformer_entity_pointer.py:375-470): every
+        step runs the incremental decoder, the full-vocabulary log-probabilities, the copy mix and the arg-max of the
+        mixed row on the device.  Returns (log_probs [B, L'], ids [B, L'+1]) as DynamicConvDecoder.generate."""
+        seed = seed.to('cuda', torch.long)
+        if seed.dim() == 2:
+            seed = seed[:, -1]
+        seed = seed.contiguous()
+        B = seed.shape[0]
+        L, h = _lib.lib(), self._h()
+        ctx, keep = self._contexts(contexts, B, 1)
+        S = (C.c_int * 4)(*[ctx.S[i] for i in range(4)])
+        cids = copy_ids.to('cuda', torch.long).contiguous()
+        hd, keep2 = self._head(cids)
+        ws = self._workspace('gen_ptr', L.tnt_decoder_generate_pointer_workspace_bytes(h, B, gen_len, S, hd.d_hidden))
+        ids = torch.empty(B, gen_len + 1, dtype=torch.long, device='cuda')
+        lp = torch.empty(B, gen_len, dtype=torch.float32, device='cuda')
+        steps = C.c_int(0)
+        _lib.check(L.tnt_decoder_generate_pointer(h, _ptr(seed), C.byref(ctx), C.byref(hd), gen_len, eos, _ptr(ids),
+                                                  _ptr(lp), C.byref(steps) if trim else None, _ptr(ws), ws.numel(),
+                                                  _stream()), 'tnt_decoder_generate_pointer')
+        if trim:
+            n = steps.value
+            return lp[:, :n], ids[:, :n + 1]
+        return lp, ids
+
+    def generate_beam(self, *a, **k):
+        raise NotImplementedError('%s: beam search through the copy head is not implemented' % type(self).__name__)
+
+
+class DynamicConvDecoderEntityPointer(DynamicConvDecoderPointer):
+    """`DynamicConvDecoderEntityPointer` + the copy head of `TransformerEntityPointerModel` (ttl/tell/models/
+    decoder_entity_pointer.py:22-388, transformer_entity_pointer.py:78-79,185-261; the experiment ttl/run.sh trains):
+    a 3-source decoder (image, article, entity) whose last layer returns the ENTITY attention, and
+    p_gen = sigmoid(project_p_gens(relu(project_first_p_gens(cat(inp_embed, X))))) mixes the vocabulary distribution
+    with that attention scattered onto the entity token ids.
+    forward(prev_target, contexts, entity_tokens) -> (lprobs [B, T, V], {'attn', 'p_gens', 'predictors'})."""
+    HOST_SIDE_KEYS = ('project_p_gens.', 'project_first_p_gens.')
+
+    def __init__(self, *args, sources=('image', 'article', 'entity'), hidden=1024, **kwargs):
+        DynamicConvDecoder.__init__(self, *args, sources=sources, **kwargs)
+        if 'entity' not in self.sources:
+            raise ValueError('DynamicConvDecoderEntityPointer needs an "entity" source')
+        dev = next(self.parameters()).device
+        self.hidden = hidden
+        _register(self, 'project_first_p_gens.bias', torch.zeros(hidden, device=dev))
+        _register(self, 'project_first_p_gens.weight_g', torch.ones(hidden, 1, device=dev))
+        _register(self, 'project_first_p_gens.weight_v', torch.zeros(hidden, 2 * self.d, device=dev))
+        _register(self, 'project_p_gens.bias', torch.zeros(1, device=dev))
+        _register(self, 'project_p_gens.weight_g', torch.ones(1, 1, device=dev))
+        _register(self, 'project_p_gens.weight_v', torch.zeros(1, hidden, device=dev))
+
+    def _first(self):
+        from . import ops
+        f = self.project_first_p_gens
+        w1 = ops.wn_fold(f.weight_v.detach(), f.weight_g.detach(), dtype=self.torch_dtype)       # [hidden, 2d]
+        return w1, f.bias.detach().float().contiguous()
+
+    def _p_gen_inputs(self, X, emb, B, T):
+        from . import ops
+        # predictors = cat(inp_embed, X) (decoder_entity_pointer.py:144); hidden = relu(project_first_p_gens(.))
+        pred = torch.cat((emb.view(T, B, self.d).transpose(0, 1), X), 2).contiguous().view(B * T, 2 * self.d)
+        w1, b1 = self._first()
+        hid = ops.linear(pred, w1, b1, epilogue=ops.EPI_RELU)
+        pg = self.project_p_gens
+        w2 = ops.wn_fold(pg.weight_v.detach(), pg.weight_g.detach()).view(-1).contiguous()        # fp32 [hidden]
+        self._predictors = pred.view(B, T, 2 * self.d)
+        return hid, self.hidden, None, 0, w2, float(pg.bias.item()), self.hidden, [hid, w2]
+
+    def forward(self, prev_target, contexts, entity_tokens, incremental_state=None, need_attn=True):
+        lp, extra = super().forward(prev_target, contexts, entity_tokens, incremental_state, need_attn)
+        extra['predictors'] = self._predictors
+        return lp, extra
+
+    def _head(self, copy_ids):
+        hd, keep = super()._head(copy_ids)
+        w1, b1 = self._first()
+        hd.w_hidden, hd.b_hidden, hd.d_hidden = w1.data_ptr(), b1.data_ptr(), self.hidden
+        return hd, keep + [w1, b1]
 
 
 class AdaptiveLoss(nn.Module):

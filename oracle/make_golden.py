@@ -171,12 +171,61 @@ def pointer_case():
     art_ids[:, 7] = art_ids[:, 1]
     lp, ex = dec({'roberta': prev}, ctx, art_ids)
     loss = F.nll_loss(lp.view(-1, V), tgt.view(-1), ignore_index=1, reduction='sum')
+    # greedy generation through the unmodified model `_generate` (transformer_context_pointer.py:467-560, sampling_topk = 1)
+    m = object.__new__(ri.load_context_pointer_model_class())
+    torch.nn.Module.__init__(m)
+    m.decoder, m.index, m.padding_idx, m.sampling_topk, m.sampling_temp = dec, 'roberta', 1, 1, 1.0
+    m.eval()
+    gen_ids_in = art_ids.clone()
+    gen_ids_in[:, :2] = 2                                      # EOS among the copy candidates
+    gen_lp, gen_ids = m._generate(prev[:, :1].clone(), ctx, gen_ids_in)
     fix = dict(config=dict(n_sources=2, sources=['image', 'article'], d=d, heads=H, ffn=64, kernels=[3, 7], vocab=V,
                            cutoffs=list(cut) + [V]),
                state_dict={k: v.clone() for k, v in dec.state_dict().items()}, prev=prev, target=tgt, contexts=ctx,
-               article_ids=art_ids, lprobs=lp, attn=ex['attn'], loss=loss, ntokens=int((tgt != 1).sum()))
+               article_ids=art_ids, lprobs=lp, attn=ex['attn'], loss=loss, ntokens=int((tgt != 1).sum()),
+               gen_article_ids=gen_ids_in, gen_logp=gen_lp, gen_ids=gen_ids)
     torch.save(fix, os.path.join(OUT, 'pointer_small.pt'))
     print('pointer_small.pt loss', float(loss), os.path.getsize(os.path.join(OUT, 'pointer_small.pt')) // 1024, 'KiB')
+
+
+def entity_pointer_case():
+    """Row f4: the unmodified DynamicConvDecoderEntityPointer (decoder_entity_pointer.py) under the unmodified
+    TransformerEntityPointerModel.output_layer / ._generate (transformer_entity_pointer.py:185-261, 375-470)."""
+    import torch.nn.functional as F
+    R = ri.load_tell()
+    d, H, V, cut, hidden = 32, 4, 300, (100, 200), 24
+    dec = ri.build_ref_decoder('entity_pointer', d=d, heads=H, ffn=64, kernels=(3, 7), vocab=V, cutoff=cut, seed=19)
+    m = object.__new__(ri.load_entity_pointer_model_class())
+    torch.nn.Module.__init__(m)
+    m.decoder = dec
+    torch.manual_seed(3)
+    m.project_first_p_gens = R.GehringLinear(2 * d, hidden, dropout=0.1)
+    m.project_p_gens = R.GehringLinear(hidden, 1)
+    m.project_first_p_gens.weight_v.normal_(0, 0.3)
+    m.project_p_gens.weight_v.normal_(0, 0.6)
+    m.project_p_gens.bias.fill_(-0.2)
+    m.relu_dropout, m.vocab_size, m.index, m.padding_idx, m.sampling_topk, m.sampling_temp = 0.1, V, 'roberta', 1, 1, 1.0
+    m.eval()
+    sources = ('image', 'article', 'entity')
+    prev, tgt, ctx = synth.make_batch(4, 10, V, sources, S_img=5, S_art=12, S_ent=9, d_ent=1024)
+    ent = torch.randint(0, V, (4, 9), generator=torch.Generator().manual_seed(7))
+    ent[:, 5] = ent[:, 0]
+    out = dec({'roberta': prev}, ctx)
+    lp = m.output_layer(out, ent)
+    loss = F.nll_loss(lp.view(-1, V), tgt.view(-1), ignore_index=1, reduction='sum')
+    gen_ent = ent.clone()
+    gen_ent[:, :2] = 2
+    gen_lp, gen_ids = m._generate(prev[:, :1].clone(), ctx, gen_ent)
+    sd = {k: v.clone() for k, v in dec.state_dict().items()}
+    sd.update({k: v.clone() for k, v in m.state_dict().items() if k.startswith('project_')})
+    fix = dict(config=dict(sources=list(sources), d=d, heads=H, ffn=64, kernels=[3, 7], vocab=V, cutoffs=list(cut) + [V],
+                           hidden=hidden),
+               state_dict=sd, prev=prev, target=tgt, contexts=ctx, entity_tokens=ent, lprobs=lp, attn=out[1]['attn'],
+               predictors=out[1]['predictors'], loss=loss, ntokens=int((tgt != 1).sum()),
+               gen_entity_tokens=gen_ent, gen_logp=gen_lp, gen_ids=gen_ids)
+    torch.save(fix, os.path.join(OUT, 'entity_pointer_small.pt'))
+    print('entity_pointer_small.pt loss', float(loss), 'gen', tuple(gen_ids.shape),
+          os.path.getsize(os.path.join(OUT, 'entity_pointer_small.pt')) // 1024, 'KiB')
 
 
 def main():
@@ -191,6 +240,7 @@ def main():
     mha_cases()
     v2_case()
     pointer_case()
+    entity_pointer_case()
 
 
 if __name__ == '__main__':

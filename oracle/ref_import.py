@@ -91,8 +91,10 @@ def load_tell():
     dec2 = importlib.import_module('tell.models.decoder_flattened')
     dec4 = importlib.import_module('tell.models.decoder_faces_objects')
     decp = importlib.import_module('tell.models.decoder_pointer')
+    dece = importlib.import_module('tell.models.decoder_entity_pointer')
     ns = types.SimpleNamespace(
         DynamicConvDecoderPointer=decp.DynamicConvDecoderPointer,
+        DynamicConvDecoderEntityPointer=dece.DynamicConvDecoderEntityPointer,
         DynamicConv1dTBC=M.DynamicConv1dTBC, MultiHeadAttention=M.MultiHeadAttention,
         AdaptiveSoftmax=M.AdaptiveSoftmax, GehringLinear=M.GehringLinear,
         AdaptiveLoss=AdaptiveLoss, AdaptiveEmbedding=AdaptiveEmbedding,
@@ -128,6 +130,23 @@ def load_faces_objects_model_class():
         _mod('pycocoevalcap.bleu.bleu_scorer', BleuScorer=object)
     mod = importlib.import_module('tell.models.transformer_faces_objects')
     return mod.TransformerFacesObjectModel
+
+
+def load_entity_pointer_model_class():
+    """The unmodified `TransformerEntityPointerModel` class (ttl/tell/models/transformer_entity_pointer.py) with the
+    AllenNLP / pycocoevalcap bases stubbed: its `output_layer` (:185-261) and `_generate` (:375-470) are run on an
+    instance whose decoder is the real reference decoder and whose RoBERTa / ResNet members are absent."""
+    load_faces_objects_model_class()      # registers the allennlp.models / pycocoevalcap stubs
+    mod = importlib.import_module('tell.models.transformer_entity_pointer')
+    return mod.TransformerEntityPointerModel
+
+
+def load_context_pointer_model_class():
+    """The unmodified model class of ttl/tell/models/transformer_context_pointer.py (the model that owns
+    DynamicConvDecoderPointer); only its `_generate` (:467-560) is run, on an instance holding the reference decoder."""
+    load_faces_objects_model_class()
+    mod = importlib.import_module('tell.models.transformer_context_pointer')
+    return mod.TransformerContextPointerModel
 
 
 def load_final_v2(variant='final_roberta2'):
@@ -176,6 +195,8 @@ def build_ref_decoder(n_sources=2, d=1024, heads=16, ffn=4096, kernels=(3, 7, 15
         dec = R.DynamicConvFacesObjectsDecoder(**common)
     elif n_sources == 'pointer':      # 2 sources + copy head (decoder_pointer.py)
         dec = R.DynamicConvDecoderPointer(article_embed_size=article_dim, **common)
+    elif n_sources == 'entity_pointer':   # image + article + entity, returns the entity attention (decoder_entity_pointer.py)
+        dec = R.DynamicConvDecoderEntityPointer(article_embed_size=article_dim, **common)
     else:
         raise ValueError(n_sources)
     dec.eval()

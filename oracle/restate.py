@@ -232,7 +232,7 @@ def decoder_layer(X: torch.Tensor, contexts: dict, sd: SD, p: str, H: int, K: in
         if drop is not None:      # element (t, b, c) of source si has counter index (t*B + b)*(ns*d) + si*d + c
             idx = (torch.arange(Tn * Bn)[:, None] * (ns * dm) + si * dm + torch.arange(dm)[None, :]).view(Tn, Bn, dm)
             a = drop(a, drop.dropout, site(DROP_ATTN_OUT), idx)
-        if s == 'article':
+        if s == 'entity' or (s == 'article' and 'entity' not in sources):   # decoder_entity_pointer.py:326-334: the entity attention is returned
             attn = w
         outs.append(layer_norm(X + a, sd, p + 'context_attn_lns.%s.' % s))
     X = gehring_linear(torch.cat(outs, -1), sd, p + 'context_fc.')
@@ -400,12 +400,7 @@ def pointer_output_layer(X: torch.Tensor, inp_embed: torch.Tensor, attn: torch.T
     (1 - sigmoid(p_gens)) * attn[:, :, :-2]; lprobs = log(clamp(probs, 1e-10, 1)).  X, inp_embed [B,T,d]; attn [B,T,S+2]
     (head-averaged article attention of the last layer); article_ids [B,S].  Returns (lprobs [B,T,V], p_gen [B,T,1])."""
     p_gens = torch.sigmoid(gehring_linear(torch.cat((inp_embed, X), 2), sd, 'project_p_gens.'))
-    gen = adaptive_log_prob(X, sd, cutoffs).exp() * p_gens
-    B, T, V = gen.shape
-    copy = attn[:, :, :-2].float() * (1 - p_gens)
-    index = article_ids[:, None, :].expand(B, T, article_ids.shape[1])
-    dist = torch.zeros(B, T, V).scatter_add_(2, index.long(), copy)
-    return (gen + dist).clamp(1e-10, 1.0).log(), p_gens
+    return copy_mix(adaptive_log_prob(X, sd, cutoffs).exp(), p_gens, attn, article_ids), p_gens
 
 
 def pointer_decoder_forward(ids: torch.Tensor, contexts: dict, article_ids: torch.Tensor, sd: SD, H: int,
@@ -414,6 +409,65 @@ def pointer_decoder_forward(ids: torch.Tensor, contexts: dict, article_ids: torc
     X, attn = decoder_forward(ids, contexts, sd, H, cutoffs, ('image', 'article'))
     lp, pg = pointer_output_layer(X, embed(ids, sd, cutoffs), attn, article_ids, sd, cutoffs)
     return lp, attn, pg
+
+
+ENTITY_SOURCES = ('image', 'article', 'entity')
+
+
+def copy_mix(gen_probs: torch.Tensor, p_gens: torch.Tensor, attn: torch.Tensor, copy_ids: torch.Tensor) -> torch.Tensor:
+    """The mix shared by both pointer heads (decoder_pointer.py:176-216 / transformer_entity_pointer.py:212-261):
+    log(clamp(p_gen * gen + scatter_add(copy_ids, (1 - p_gen) * attn[:, :, :-2]), 1e-10, 1))."""
+    B, T, V = gen_probs.shape
+    copy = attn[:, :, :-2].float() * (1 - p_gens)
+    index = copy_ids[:, None, :].expand(B, T, copy_ids.shape[1])
+    dist = torch.zeros(B, T, V).scatter_add_(2, index.long(), copy)
+    return (gen_probs * p_gens + dist).clamp(1e-10, 1.0).log()
+
+
+def entity_pointer_output_layer(X: torch.Tensor, inp_embed: torch.Tensor, attn: torch.Tensor, entity_tokens: torch.Tensor,
+                                sd: SD, cutoffs: Sequence[int]):
+    """Copy head of TransformerEntityPointerModel.output_layer (transformer_entity_pointer.py:185-261), eval mode:
+    p_gens = sigmoid(project_p_gens(relu(project_first_p_gens(predictors)))), predictors = cat(inp_embed, X)
+    (decoder_entity_pointer.py:144); attn = the ENTITY attention of the last layer (decoder_entity_pointer.py:326-334).
+    `sd` holds the decoder's keys plus the model's `project_first_p_gens.*` / `project_p_gens.*`."""
+    hid = torch.relu(gehring_linear(torch.cat((inp_embed, X), 2), sd, 'project_first_p_gens.'))
+    p_gens = torch.sigmoid(gehring_linear(hid, sd, 'project_p_gens.'))
+    return copy_mix(adaptive_log_prob(X, sd, cutoffs).exp(), p_gens, attn, entity_tokens), p_gens
+
+
+def entity_pointer_forward(ids: torch.Tensor, contexts: dict, entity_tokens: torch.Tensor, sd: SD, H: int,
+                           cutoffs: Sequence[int]):
+    """DynamicConvDecoderEntityPointer.forward (decoder_entity_pointer.py:97-145) + the model's output_layer."""
+    X, attn = decoder_forward(ids, contexts, sd, H, cutoffs, ENTITY_SOURCES)
+    lp, pg = entity_pointer_output_layer(X, embed(ids, sd, cutoffs), attn, entity_tokens, sd, cutoffs)
+    return lp, attn, pg
+
+
+def pointer_greedy_generate(seed_ids: torch.Tensor, contexts: dict, copy_ids: torch.Tensor, sd: SD, H: int,
+                            cutoffs: Sequence[int], entity: bool = False, gen_len: int = 100, eos: int = 2, pad: int = 1):
+    """`_generate` of the pointer models with sampling_topk = 1 (transformer_entity_pointer.py:375-470; the context
+    pointer model runs the same loop over the article ids): per step the incremental decoder, the copy head on the
+    step's (X, inp_embed, attn), arg-max of the mixed log-probabilities.  Finished rows are masked instead of dropped
+    (rows are independent).  Returns (log_probs [B, L], token_ids [B, L+1])."""
+    sources = ENTITY_SOURCES if entity else ('image', 'article')
+    head = entity_pointer_output_layer if entity else pointer_output_layer
+    state: dict = {}
+    active = seed_ids[:, -1] != eos
+    toks, lps = [seed_ids[:, :1]], []
+    cur = seed_ids[:, :1]
+    for _ in range(gen_len):
+        start = state.get('pos', 0)
+        X, attn = decoder_forward(cur, contexts, sd, H, cutoffs, sources, state)
+        lp, _ = head(X[:, -1:], embed(cur, sd, cutoffs, start)[:, -1:], attn[:, -1:], copy_ids, sd, cutoffs)
+        best_lp, best = lp[:, 0].max(-1)
+        tok = torch.where(active, best, torch.full_like(best, pad))
+        lps.append(torch.where(active, best_lp, torch.zeros_like(best_lp))[:, None])
+        toks.append(tok[:, None])
+        active = active & (best != eos)
+        cur = best[:, None]
+        if not bool(active.any()):
+            break
+    return torch.cat(lps, 1), torch.cat(toks, 1)
 
 
 def greedy_generate(seed_ids: torch.Tensor, contexts: dict, sd: SD, H: int,

@@ -26,7 +26,7 @@ def caption_ids(B, T, vocab, g, ragged=True):
 
 
 def contexts(B, g, sources=('image', 'article'), S_img=49, S_art=512, S_faces=4, S_obj=64,
-             d_img=2048, d_art=1024, d_faces=512, d_obj=2048):
+             d_img=2048, d_art=1024, d_faces=512, d_obj=2048, S_ent=32, d_ent=1024):
     """contexts dict in the reference layout: src [S,B,kdim] float, src_mask [B,S] bool True=pad."""
     ctx = {}
     if 'image' in sources:
@@ -39,6 +39,11 @@ def contexts(B, g, sources=('image', 'article'), S_img=49, S_art=512, S_faces=4,
         m = torch.arange(S_art)[None, :] >= n[:, None]
         a = a.masked_fill(m.t()[:, :, None], 0.0)
         ctx['article'], ctx['article_mask'] = a, m
+    if 'entity' in sources:      # entity-token embeddings; a row may have no entity at all (transformer_entity_pointer.py:354-355)
+        e = torch.randn(S_ent, B, d_ent, generator=g)
+        n = torch.randint(0, S_ent + 1, (B,), generator=g)
+        m = torch.arange(S_ent)[None, :] >= n[:, None]
+        ctx['entity'], ctx['entity_mask'] = e.masked_fill(m.t()[:, :, None], 0.0), m
     if 'faces' in sources:
         f = torch.randn(S_faces, B, d_faces, generator=g)
         f = f / f.norm(dim=-1, keepdim=True)

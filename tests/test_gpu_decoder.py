@@ -88,8 +88,53 @@ def test_pointer_decoder_golden(dtype):
     out = dec.nll(lp, f['target'].cuda())
     assert int(out[1].item()) == f['ntokens']
     assert abs(out[0].item() - f['loss'].item()) < tol * abs(f['loss'].item())
+    _check_pointer_generation(dec, f, f['gen_article_ids'], dtype)
+
+
+def _check_pointer_generation(dec, f, copy_ids, dtype):
+    """Greedy generation through the copy head against the ids / log-probs the unmodified reference `_generate`
+    produced (100 steps, rows that copy EOS finish early): bit-exact ids in fp32; in bf16 the first step's choice and
+    log-prob (later steps may legitimately fork on near-ties)."""
+    L = f['gen_ids'].shape[1] - 1
+    lp, ids = dec.generate(f['prev'][:, :1].cuda(), cuda_ctx(f['contexts']), copy_ids.cuda(), gen_len=100)
+    if dtype == torch.float32:
+        assert ids.shape[1] == L + 1
+        assert torch.equal(ids.cpu(), f['gen_ids'])
+        assert (lp.cpu() - f['gen_logp']).abs().max().item() < 1e-3
+    else:
+        assert torch.equal(ids.cpu()[:, 1], f['gen_ids'][:, 1])
+        assert (lp.cpu()[:, 0] - f['gen_logp'][:, 0]).abs().max().item() < 1e-1
     with pytest.raises(NotImplementedError):
-        dec.generate(f['prev'][:, :1].cuda(), cuda_ctx(f['contexts']))
+        dec.generate_beam(f['prev'][:, :1].cuda(), cuda_ctx(f['contexts']))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_entity_pointer_decoder_golden(dtype):
+    """Row f4 (decoder_entity_pointer.py + transformer_entity_pointer.py output_layer / _generate): the 3-source decoder
+    that returns the ENTITY attention, the two-layer p_gen head, the copy mix over the entity token ids, the model's
+    nll_loss and greedy generation, against the fixture frozen from the unmodified reference."""
+    from news_image_caption_b200 import DynamicConvDecoderEntityPointer, build
+    build.build()
+    f = torch.load(os.path.join(G, 'entity_pointer_small.pt'), weights_only=False)
+    cfg = f['config']
+    dec = DynamicConvDecoderEntityPointer(decoder_output_dim=cfg['d'], decoder_attention_heads=cfg['heads'],
+                                          decoder_ffn_embed_dim=cfg['ffn'], decoder_kernel_size_list=cfg['kernels'],
+                                          vocab_size=cfg['vocab'], adaptive_softmax_cutoff=cfg['cutoffs'][:-1],
+                                          sources=cfg['sources'], hidden=cfg['hidden'], dtype=dtype)
+    dec.load_reference_state_dict(f['state_dict'])
+    lp, ex = dec({'roberta': f['prev'].cuda()}, cuda_ctx(f['contexts']), f['entity_tokens'].cuda())
+    tol = 1e-4 if dtype == torch.float32 else 2e-2
+    assert lp.shape == f['lprobs'].shape
+    assert rel_err(lp.exp(), f['lprobs'].exp()) < tol
+    big = f['lprobs'] > -12
+    assert (lp.cpu()[big] - f['lprobs'][big]).abs().max().item() < (1e-3 if dtype == torch.float32 else 1e-1)
+    assert rel_err(ex['attn'], f['attn']) < tol
+    assert rel_err(ex['predictors'], f['predictors']) < tol
+    out = dec.nll(lp, f['target'].cuda())
+    assert int(out[1].item()) == f['ntokens']
+    assert abs(out[0].item() - f['loss'].item()) < tol * abs(f['loss'].item())
+    _check_pointer_generation(dec, f, f['gen_entity_tokens'], dtype)
 
 
 def test_pointer_mix_full_vocab():

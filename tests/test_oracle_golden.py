@@ -100,3 +100,26 @@ def test_pointer_decoder():
     m = tgt != 1
     loss = -lp.view(-1, cfg['vocab'])[m, tgt[m]].sum()
     assert int(m.sum()) == f['ntokens'] and abs(loss.item() - f['loss'].item()) < 1e-4 * abs(f['loss'].item())
+    glp, gids = O.pointer_greedy_generate(f['prev'][:, :1], f['contexts'], f['gen_article_ids'], f['state_dict'],
+                                          cfg['heads'], cfg['cutoffs'])
+    assert torch.equal(gids, f['gen_ids'])
+    close(glp, f['gen_logp'])
+
+
+def test_entity_pointer_decoder():
+    """Row f4: the oracle's 3-source entity-pointer decoder + copy head and its greedy generation against the fixture
+    frozen from the unmodified DynamicConvDecoderEntityPointer / TransformerEntityPointerModel."""
+    f = load('entity_pointer_small.pt')
+    cfg = f['config']
+    lp, attn, pg = O.entity_pointer_forward(f['prev'], f['contexts'], f['entity_tokens'], f['state_dict'], cfg['heads'],
+                                            cfg['cutoffs'])
+    close(lp, f['lprobs'])
+    close(attn, f['attn'])
+    tgt = f['target'].view(-1)
+    m = tgt != 1
+    loss = -lp.view(-1, cfg['vocab'])[m, tgt[m]].sum()
+    assert int(m.sum()) == f['ntokens'] and abs(loss.item() - f['loss'].item()) < 1e-4 * abs(f['loss'].item())
+    glp, gids = O.pointer_greedy_generate(f['prev'][:, :1], f['contexts'], f['gen_entity_tokens'], f['state_dict'],
+                                          cfg['heads'], cfg['cutoffs'], entity=True)
+    assert torch.equal(gids, f['gen_ids'])
+    close(glp, f['gen_logp'])

@@ -307,3 +307,65 @@ def test_beam_search_matches_reference(monkeypatch, seed, eos_bias):
     if eos_bias < -10:
         for r, m in zip(ref, mine):
             assert torch.equal(r['seq'], m['seq'])
+
+
+def _entity_pointer_reference(d=64, H=8, V=500, cut=(120, 300), hidden=48, seed=17):
+    """The unmodified entity-pointer decoder + an instance of the unmodified TransformerEntityPointerModel class that
+    holds it (the class's own __init__ needs the RoBERTa / ResNet hubs and hard-codes 2048 -> 1024 head sizes)."""
+    R = ri.load_tell()
+    Cls = ri.load_entity_pointer_model_class()
+    dec = ri.build_ref_decoder('entity_pointer', d=d, heads=H, ffn=96, kernels=(3, 15), vocab=V, cutoff=cut, seed=seed)
+    m = object.__new__(Cls)
+    torch.nn.Module.__init__(m)
+    m.decoder = dec
+    torch.manual_seed(seed + 1)
+    m.project_first_p_gens = R.GehringLinear(2 * d, hidden, dropout=0.1)
+    m.project_p_gens = R.GehringLinear(hidden, 1)
+    m.project_first_p_gens.weight_v.normal_(0, 0.2)
+    m.project_p_gens.weight_v.normal_(0, 0.5)
+    m.project_p_gens.bias.fill_(0.1)
+    m.relu_dropout, m.vocab_size, m.index, m.padding_idx = 0.1, V, 'roberta', 1
+    m.sampling_topk, m.sampling_temp = 1, 1.0
+    m.eval()
+    sd = dict(dec.state_dict())
+    for k, v in m.state_dict().items():
+        if k.startswith('project_'):
+            sd[k] = v
+    return m, sd
+
+
+def test_entity_pointer_decoder_matches_reference():
+    """Row f4: the 3-source entity-pointer decoder (decoder_entity_pointer.py) and the model's copy head
+    (transformer_entity_pointer.py:185-261, unmodified) against the oracle's entity_pointer_forward."""
+    torch.set_grad_enabled(False)
+    d, H, V, cut = 64, 8, 500, (120, 300)
+    m, sd = _entity_pointer_reference(d, H, V, cut)
+    prev, tgt, ctx = synth.make_batch(4, 9, V, O.ENTITY_SOURCES, seed=23, S_img=4, S_art=17, S_ent=11, d_ent=1024)
+    ctx['sections'], ctx['sections_mask'] = None, None
+    ent = torch.randint(0, V, (4, 11), generator=torch.Generator().manual_seed(4))
+    ent[:, 6] = ent[:, 1]                                       # an entity token that occurs twice
+    out = m.decoder({'roberta': prev}, ctx)
+    lp = m.output_layer(out, ent)
+    lo, attn, pg = O.entity_pointer_forward(prev, ctx, ent, sd, H, list(cut) + [V])
+    close(attn, out[1]['attn'])
+    close(lo, lp)
+    assert (pg > 0.05).all() and (pg < 0.95).all()
+    torch.set_grad_enabled(True)
+
+
+def test_pointer_greedy_generation_matches_reference():
+    """The unmodified `_generate` loop of the entity-pointer model (transformer_entity_pointer.py:375-470; 100 steps,
+    sampling_topk = 1 so the multinomial draw is deterministic) against the oracle's pointer_greedy_generate."""
+    torch.set_grad_enabled(False)
+    d, H, V, cut = 64, 8, 500, (120, 300)
+    m, sd = _entity_pointer_reference(d, H, V, cut, seed=29)
+    sd['adaptive_softmax.head.class_proj.weight'] *= 0.2       # keep most of the mass in the head: EOS (id 2) can win
+    m.decoder.load_state_dict(sd, strict=False)
+    prev, _, ctx = synth.make_batch(5, 3, V, O.ENTITY_SOURCES, seed=31, S_img=4, S_art=17, S_ent=11, d_ent=1024)
+    ent = torch.randint(0, V, (5, 11), generator=torch.Generator().manual_seed(6))
+    ent[:, :3] = 2                                              # EOS among the copy candidates: some rows finish early
+    lp_r, ids_r = m._generate(prev[:, :1].clone(), ctx, ent)
+    lp_o, ids_o = O.pointer_greedy_generate(prev[:, :1], ctx, ent, sd, H, list(cut) + [V], entity=True)
+    assert ids_r.shape == ids_o.shape and torch.equal(ids_r, ids_o)
+    close(lp_o, lp_r)
+    torch.set_grad_enabled(True)
