@@ -47,8 +47,11 @@ struct StepBatch {
   const int* order[TNT_MAX_SOURCES];      // optional per source: caption slots sorted by live keys, longest first
   int n;
   int* sched;
+  float* scores;      // SCORES only: [B, H, S] log2-domain scores of source `scores_src` (live keys), for the head-averaged weights
+  int scores_src;
 };
 
+template <bool SCORES>
 __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(const __grid_constant__ StepBatch batch) {
   __shared__ float sm_m[kWarps][32], sm_l[kWarps][32];
   __shared__ float sm_acc[kWarps][32][17];
@@ -133,6 +136,8 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(const __grid_co
         for (int i = 0; i < 16; ++i) s = fmaf(q[i], kf[i], s);
         s += __shfl_xor_sync(0xffffffffu, s, 1);
         s += __shfl_xor_sync(0xffffffffu, s, 2);
+        if (SCORES && src == batch.scores_src && (lane & 3) == 0)
+          batch.scores[(static_cast<long>(b) * p.H + h) * S + sm_live[j0 + u * kWarps]] = s;
         const float mn = fmaxf(m, s);
         const float corr = exp2f(m - mn), pe = exp2f(s - mn);
         l = l * corr + pe;
@@ -194,7 +199,8 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(const __grid_co
 
 }  // namespace
 
-int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched = nullptr, const int* const* orders = nullptr);
+int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched = nullptr, const int* const* orders = nullptr,
+                         float* scores = nullptr, int scores_src = -1, float* weights_out = nullptr);
 
 bool xattn_step_supported(const tnt_xattn_params* p) {
   if (p->T != 1 || p->dtype != TNT_BF16 || p->D != 64 || (p->H % kHeadsPerCta) != 0 || p->n_extra != 0 || p->weights || p->drop.p > 0.f)
@@ -219,6 +225,24 @@ __global__ void __launch_bounds__(1024) live_order_kernel(const uint32_t* tile_l
     order[rank] = b;
   }
 }
+
+// head-averaged attention weights of a decode step (multi_head.py:478-484) from the step kernel's score dump:
+// weights[b, s] = (1/H) sum_h exp2(score[b, h, s] - lse2[b, h]); 0 for padded keys
+__global__ void __launch_bounds__(256) step_weights_kernel(const float* scores, const float* lse, const uint8_t* mask, long m_stride_b,
+                                                           int B, int H, int S, int SM, float* weights) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= B * S) return;
+  const int b = i / S, sx = i - b * S;
+  float w = 0.f;
+  if (!(sx < SM && mask[static_cast<long>(b) * m_stride_b + sx])) {
+    for (int h = 0; h < H; ++h) {
+      const float l = lse[static_cast<long>(b) * H + h];
+      w += exp2f(scores[(static_cast<long>(b) * H + h) * S + sx] - l * 1.4426950408889634f);
+    }
+    w /= static_cast<float>(H);
+  }
+  weights[i] = w;
+}
 }  // namespace
 
 int xattn_live_order(const uint32_t* tile_live, int B, int* order, cudaStream_t st) {
@@ -228,7 +252,9 @@ int xattn_live_order(const uint32_t* tile_live, int B, int* order, cudaStream_t 
 }
 
 // n problems with the same B and H (the sources of one decoder layer), one launch
-int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched, const int* const* orders) {
+// `scores` (scratch [B, H, S] fp32) + `weights_out` [B, S]: also return the head-averaged weights of problem `scores_src`
+int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched, const int* const* orders, float* scores,
+                         int scores_src, float* weights_out) {
   TNT_CHECK_ARG(n >= 1 && n <= TNT_MAX_SOURCES, "xattn_step: %d problems", n);
   StepBatch batch;
   int order[TNT_MAX_SOURCES];
@@ -242,6 +268,14 @@ int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int
     batch.order[i] = (orders && ps[order[i]].kv_group <= 1) ? orders[order[i]] : nullptr;
   }
   batch.n = n;
+  batch.scores = nullptr;
+  batch.scores_src = -1;
+  if (scores && weights_out && scores_src >= 0) {
+    TNT_CHECK_ARG(scores_src < n && ps[scores_src].kv_group <= 1 && ps[scores_src].lse, "xattn_step: weights need kv_group 1 and an LSE buffer");
+    batch.scores = scores;
+    for (int i = 0; i < n; ++i)
+      if (order[i] == scores_src) batch.scores_src = i;
+  }
   // measured (B = 256, generation bench): pulling items is no faster than one CTA per item (27.7 vs 27.5 ms) -- all 1024 CTAs
   // are co-resident anyway -- so the static mapping stays the default; TNT_STEP_ATTN_DYNAMIC=1 switches the queue on
   static const bool dyn = [] { const char* e = getenv("TNT_STEP_ATTN_DYNAMIC"); return e && e[0] == '1'; }();
@@ -249,7 +283,16 @@ int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int
   const int total = n * ps[0].B * (ps[0].H / kHeadsPerCta);
   static const int per_sm = [] { const char* e = getenv("TNT_STEP_ATTN_CTAS_PER_SM"); return e ? std::max(1, atoi(e)) : 4; }();
   dim3 grid(batch.sched ? std::min(total, per_sm * num_sms()) : total);
-  TNT_CUDA(launch_pdl(xattn_step_kernel, grid, dim3(kWarps * 32), 0, st, 1, batch));
+  if (batch.scores) {
+    TNT_CUDA(launch_pdl(xattn_step_kernel<true>, grid, dim3(kWarps * 32), 0, st, 1, batch));
+    TNT_LAUNCHED();
+    const tnt_xattn_params& q = ps[scores_src];
+    const int SM = q.mask_mode == TNT_MASK_KEY_PADDING ? (q.mask_S > 0 ? std::min(q.mask_S, q.S) : q.S) : 0;
+    step_weights_kernel<<<(q.B * q.S + 255) / 256, 256, 0, st>>>(scores, q.lse, q.mask, q.m_stride_b, q.B, q.H, q.S, SM, weights_out);
+    TNT_LAUNCHED();
+    return TNT_OK;
+  }
+  TNT_CUDA(launch_pdl(xattn_step_kernel<false>, grid, dim3(kWarps * 32), 0, st, 1, batch));
   TNT_LAUNCHED();
   return TNT_OK;
 }

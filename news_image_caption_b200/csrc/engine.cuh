@@ -88,6 +88,8 @@ struct FwdWs {
   uint32_t* tile_live[TNT_MAX_SOURCES];   // [B_kv] live 128-key tiles of every context entry (project_kv fills it)
   int* order[TNT_MAX_SOURCES];   // decode engines: context entries sorted by live keys, longest first (or NULL)
   int* sched;                    // 2 zeroed ints: dynamic work counters of the decode-step attention (or NULL)
+  float* step_scores = nullptr;  // generation through the copy head: [B, H, S_w + 2] score dump of the decode-step attention
+  float* step_lse = nullptr;     //   and its [B, H] log-sum-exp
   size_t total;
 };
 // B_kv >= 0: number of context entries the K/V cache holds when it differs from the row batch B (beam search)

@@ -10,7 +10,8 @@ namespace tnt {
 int xattn_check(const tnt_xattn_params* p);
 int xattn_fwd_dispatch(const tnt_xattn_params* p, cudaStream_t st);
 bool xattn_step_supported(const tnt_xattn_params* p);
-int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched = nullptr, const int* const* orders = nullptr);
+int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int* sched = nullptr, const int* const* orders = nullptr,
+                         float* scores = nullptr, int scores_src = -1, float* weights_out = nullptr);
 int xattn_live_order(const uint32_t* tile_live, int B, int* order, cudaStream_t st);
 bool xattn_force_simt();
 
@@ -181,8 +182,11 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     ap.o_stride_t = ap.q_stride_t; ap.o_stride_b = ap.q_stride_b;
     ap.mask = ctx->pad_mask[s]; ap.m_stride_b = ctx->S[s]; ap.m_stride_t = 0;
     ap.mask_mode = (ctx->pad_mask[s] && ctx->S[s] > 0) ? TNT_MASK_KEY_PADDING : TNT_MASK_NONE;
-    ap.weights = (attn_out && s == D->article_idx) ? attn_out : nullptr;
-    ap.lse = w.lse[s];
+    // decode step with a score scratch (generation through the copy head): the step kernel dumps its scores and a small
+    // kernel head-averages them, so the layer stays on the one-launch step path
+    const bool step_weights = T == 1 && w.step_scores && attn_out && s == D->article_idx;
+    ap.weights = (attn_out && s == D->article_idx && !step_weights) ? attn_out : nullptr;
+    ap.lse = step_weights ? w.step_lse : w.lse[s];
     // the K/V buffer carries the 2 extra rows (project_kv), so they are plain keys the mask does not cover
     ap.B = B; ap.T = T; ap.S = ctx->S[s] + 2; ap.H = H; ap.D = d / H; ap.n_extra = 0;
     ap.mask_S = ctx->S[s];
@@ -196,12 +200,15 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     TNT_TRY(xattn_check(&ap));
     all_step = all_step && !xattn_force_simt() && xattn_step_supported(&ap);
   }
+  if (!all_step && attn_out && D->article_idx >= 0) aps[D->article_idx].weights = attn_out;   // general kernels return the weights themselves
   if (all_step) {
     const int pid = prof_enabled() ? prof_begin("xattn_step.merged", st) : -1;   // -1 while a graph is being captured
     const int* orders[TNT_MAX_SOURCES];
     for (int s = 0; s < ns; ++s)
       orders[s] = (aps[s].mask_mode == TNT_MASK_KEY_PADDING && ctx->B <= 4096 && ring) ? w.order[s] : nullptr;
-    TNT_TRY(xattn_fwd_step_multi(aps, ns, st, w.sched, orders));   // decode step: every source of the layer in one launch
+    const bool sw = w.step_scores && attn_out && D->article_idx >= 0;
+    TNT_TRY(xattn_fwd_step_multi(aps, ns, st, w.sched, orders, sw ? w.step_scores : nullptr, sw ? D->article_idx : -1,
+                                 sw ? attn_out : nullptr));   // decode step: every source of the layer in one launch
     prof_end(pid, st);
   } else {
     for (int s = 0; s < ns; ++s) {

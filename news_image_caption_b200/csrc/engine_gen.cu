@@ -127,6 +127,8 @@ PtrWs carve_ptr(const tnt_decoder* D, int B, const int* S, int d_hidden, void* w
   w.lp = static_cast<float*>(take(sizeof(float) * static_cast<size_t>(B) * D->cfg.vocab));
   w.ada_bytes = adasoftmax_workspace_bytes(D->ada, B, true);
   w.ada = take(w.ada_bytes);
+  w.g.f.step_scores = static_cast<float*>(take(sizeof(float) * B * D->cfg.heads * (sw + 2)));
+  w.g.f.step_lse = static_cast<float*>(take(sizeof(float) * B * D->cfg.heads));
   w.total = off;
   return w;
 }

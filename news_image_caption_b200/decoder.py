@@ -225,7 +225,8 @@ class DynamicConvDecoder(nn.Module):
 
     # ------------------------------------------------------------------ reference API
     def forward(self, prev_target, contexts, incremental_state=None, need_attn=True):
-        """ids [B,T] (or {'roberta': ids}) -> (X [B,T,d], {'attn': [B,T,S_article+2] | None}) --
+        """ids [B,T] (or {'roberta': ids}) -> (X [B,T,d], {'attn': [B,T,S_article+2] | None}; the entity attention when
+        the decoder has an 'entity' source, decoder_entity_pointer.py:326-334) --
         decoder_flattened.py:96-146.  `incremental_state` selects single-step decoding and is handled
         by `generate()`; passing one here raises (the engine owns the incremental buffers)."""
         if incremental_state is not None:
@@ -239,8 +240,9 @@ class DynamicConvDecoder(nn.Module):
         ws = self._workspace('fwd', L.tnt_decoder_workspace_bytes(h, B, T, S))
         X = torch.empty(B, T, self.d, dtype=self.torch_dtype, device='cuda')
         attn = None
-        if need_attn and 'article' in self.sources:
-            attn = torch.empty(B, T, ctx.S[self.sources.index('article')] + 2, dtype=torch.float32, device='cuda')
+        src = 'entity' if 'entity' in self.sources else 'article'    # the source whose attention the reference's layer returns
+        if need_attn and src in self.sources:
+            attn = torch.empty(B, T, ctx.S[self.sources.index(src)] + 2, dtype=torch.float32, device='cuda')
         _lib.check(L.tnt_decoder_forward(h, _ptr(ids), C.byref(ctx), _ptr(X), _ptr(attn), _ptr(ws), ws.numel(),
                                          _stream()), 'tnt_decoder_forward')
         return X, {'attn': attn, 'inner_states': None}

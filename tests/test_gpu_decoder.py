@@ -326,3 +326,51 @@ def test_beam_search_full_size(full_model):
     lp_g, ids_g = dec16.generate(prev[:, :1].cuda(), cuda_ctx(ctx), gen_len=6, eos=-1, trim=False)
     assert torch.equal(s1[:, 0], ids_g[:, 1:])
     assert (l1[:, 0] - lp_g).abs().max().item() < 2e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('kind', ['pointer', 'entity_pointer'])
+def test_pointer_generation_step_attention_weights(kind):
+    """bf16, head dim 64: the generation loop takes the copied attention from the decode-step kernel's score dump
+    (attention_step.cu, step_weights_kernel).  Step 0 of generate() must agree with the teacher-forced forward on the seed
+    token (general attention kernels, weights returned by the kernel itself), which in turn is checked against the oracle;
+    p_gen is biased towards copying so the chosen token depends on the attention weights."""
+    from news_image_caption_b200 import DynamicConvDecoderEntityPointer, DynamicConvDecoderPointer, build
+    from news_image_caption_b200.decoder import random_state_dict
+    from oracle import restate as O
+    from oracle import synth
+    build.build()
+    ent = kind == 'entity_pointer'
+    sources = ('image', 'article', 'entity') if ent else ('image', 'article')
+    d, H, V, cut, hidden = 512, 8, 600, [200, 400, 600], 64
+    kw = dict(decoder_output_dim=d, decoder_attention_heads=H, decoder_ffn_embed_dim=256, decoder_kernel_size_list=[3, 7],
+              vocab_size=V, adaptive_softmax_cutoff=cut[:-1], sources=sources, dtype=torch.bfloat16)
+    dec = DynamicConvDecoderEntityPointer(hidden=hidden, **kw) if ent else DynamicConvDecoderPointer(**kw)
+    sd = random_state_dict(d=d, heads=H, ffn=256, kernels=(3, 7), vocab=V, cutoffs=cut, sources=sources, seed=3)
+    g = torch.Generator().manual_seed(8)
+    if ent:
+        sd['project_first_p_gens.weight_v'] = torch.randn(hidden, 2 * d, generator=g) * 0.05
+        sd['project_first_p_gens.weight_g'] = torch.ones(hidden, 1)
+        sd['project_first_p_gens.bias'] = torch.zeros(hidden)
+    sd['project_p_gens.weight_v'] = torch.randn(1, hidden if ent else 2 * d, generator=g) * 0.05
+    sd['project_p_gens.weight_g'] = torch.ones(1, 1)
+    sd['project_p_gens.bias'] = torch.full((1,), -2.0)
+    dec.load_reference_state_dict(sd)
+    B = 6
+    prev, _, ctx = synth.make_batch(B, 4, V, sources, seed=77, S_img=9, S_art=70, S_ent=21)
+    src = 'entity' if ent else 'article'
+    ctx[src + '_mask'][0] = False                     # a caption with no padding at all
+    copy_ids = torch.randint(3, V, (B, ctx[src].shape[0]), generator=g)
+    seed = prev[:, :1]
+    lp_fwd, _ = dec({'roberta': seed.cuda()}, cuda_ctx(ctx), copy_ids.cuda())
+    head = O.entity_pointer_forward if ent else O.pointer_decoder_forward
+    lo, _, pg = head(seed, ctx, copy_ids, {k: v.float() for k, v in sd.items()}, H, cut)
+    assert rel_err(lp_fwd.exp(), lo.exp()) < 3e-2
+    assert (pg < 0.5).all()                           # most of the mass is copied
+    lp, ids = dec.generate(seed.cuda(), cuda_ctx(ctx), copy_ids.cuda(), gen_len=3, trim=False)
+    best_lp, best = lp_fwd[:, 0].max(-1)
+    top2 = lp_fwd[:, 0].topk(2).values
+    clear = (top2[:, 0] - top2[:, 1]) > 0.05          # rows whose winner is not a near-tie
+    assert clear.sum() >= B // 2
+    assert torch.equal(ids[clear, 1], best[clear])
+    assert (lp[:, 0] - best_lp).abs().max().item() < 2e-2
