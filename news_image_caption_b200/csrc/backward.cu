@@ -80,7 +80,16 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* x, long ldx, int M
 }
 
 // ------------------------------------------------------------------------------ weight-norm backward
-// one warp per parameter row
+// one warp per parameter row; rows are walked in 1024-column chunks with all 8 float4 loads per lane (of v and of dW) in
+// flight at once -- the rolled scalar loop took 19 us per matrix, one memory latency per iteration
+__device__ __forceinline__ void ld8(const float* row, int c0, int cols, int lane, float4 (&a)[8]) {
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const int c = c0 + (u * 32 + lane) * 4;
+    a[u] = c < cols ? __ldg(reinterpret_cast<const float4*>(row + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
 __global__ void __launch_bounds__(256) wn_bwd_kernel(const float* v, const float* g, const float* dW, long lddw,
                                                      float* dv, float* dg, int rows, int cols, int glu) {
   const int lane = threadIdx.x & 31;
@@ -90,6 +99,51 @@ __global__ void __launch_bounds__(256) wn_bwd_kernel(const float* v, const float
   const float* vr = v + static_cast<long>(r) * cols;
   const float* dr = dW + static_cast<long>(rw) * lddw;
   float* o = dv + static_cast<long>(r) * cols;
+  const bool vec = (cols & 3) == 0 && (lddw & 3) == 0 && ((reinterpret_cast<uintptr_t>(v) | reinterpret_cast<uintptr_t>(dW) |
+                                                          reinterpret_cast<uintptr_t>(dv)) & 15u) == 0;
+  if (vec) {
+    float4 a[8], d[8];
+    if (!g) {
+      for (int c0 = 0; c0 < cols; c0 += 1024) {
+        ld8(dr, c0, cols, lane, d);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int c = c0 + (u * 32 + lane) * 4;
+          if (c < cols) *reinterpret_cast<float4*>(o + c) = d[u];
+        }
+      }
+      return;
+    }
+    float nn = 0.f, dot = 0.f;
+    for (int c0 = cols > 1024 ? ((cols - 1) / 1024) * 1024 : 0; c0 >= 0; c0 -= 1024) {     // chunk 0 last: it stays in registers
+      ld8(vr, c0, cols, lane, a);
+      ld8(dr, c0, cols, lane, d);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        nn = fmaf(a[u].x, a[u].x, fmaf(a[u].y, a[u].y, fmaf(a[u].z, a[u].z, fmaf(a[u].w, a[u].w, nn))));
+        dot = fmaf(a[u].x, d[u].x, fmaf(a[u].y, d[u].y, fmaf(a[u].z, d[u].z, fmaf(a[u].w, d[u].w, dot))));
+      }
+    }
+    nn = warp_sum(nn);
+    dot = warp_sum(dot);
+    const float n = sqrtf(nn), gg = g[r];
+    const float k1 = gg / n, k2 = dot / nn;
+    for (int c0 = 0; c0 < cols; c0 += 1024) {
+      if (c0 > 0) {
+        ld8(vr, c0, cols, lane, a);
+        ld8(dr, c0, cols, lane, d);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int c = c0 + (u * 32 + lane) * 4;
+        if (c < cols)
+          *reinterpret_cast<float4*>(o + c) = make_float4(k1 * (d[u].x - k2 * a[u].x), k1 * (d[u].y - k2 * a[u].y),
+                                                          k1 * (d[u].z - k2 * a[u].z), k1 * (d[u].w - k2 * a[u].w));
+      }
+    }
+    if (lane == 0) dg[r] = dot / n;
+    return;
+  }
   if (!g) {
     for (int c = lane; c < cols; c += 32) o[c] = dr[c];
     return;
