@@ -356,6 +356,28 @@ int wn_bwd(const float* v, const float* g, const float* dW, long lddw, float* dv
 }
 
 
+namespace {
+// dst[i] = sum_g parts[g * n + i]: the reduction over K-split partial weight gradients (n % 4 == 0)
+__global__ void __launch_bounds__(256) sum_partials_kernel(float* dst, const float* parts, int G, long n4) {
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < n4; i += gridDim.x * 256L) {
+    float4 a = __ldg(reinterpret_cast<const float4*>(parts) + i);
+    for (int g = 1; g < G; ++g) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(parts) + g * n4 + i);
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    reinterpret_cast<float4*>(dst)[i] = a;
+  }
+}
+}  // namespace
+
+int sum_partials(float* dst, const float* parts, int G, long n, cudaStream_t st) {
+  TNT_CHECK_ARG(dst && parts && G >= 1 && n % 4 == 0, "sum_partials: bad arguments");
+  const long n4 = n / 4;
+  sum_partials_kernel<<<static_cast<int>(std::min<long>((n4 + 255) / 256, 8L * num_sms())), 256, 0, st>>>(dst, parts, G, n4);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
 int permute_rows(const void* src, void* dst, int B, int T, int C, int dtype, bool to_tb, cudaStream_t st) {
   TNT_CHECK_ARG(src && dst && C % 8 == 0, "permute_rows: bad arguments");
   if (B * T == 0) return TNT_OK;

@@ -18,6 +18,8 @@ int colsum(const void* x, long ldx, int M, int N, const int* m_dyn, float* out, 
 
 // weight_norm backward (linear.py:30-33): w = g v / |v|_row;  dW [rows, cols] fp32 (row r of the parameter sits
 // at row glu_row(r) of dW when glu_interleave) -> dv [rows, cols], dg [rows].  g == NULL: dv = dW (plain copy).
+// dst[i] = sum over g < G of parts[g * n + i] (K-split partial weight gradients)
+int sum_partials(float* dst, const float* parts, int G, long n, cudaStream_t st);
 int wn_bwd(const float* v, const float* g, const float* dW, long lddw, float* dv, float* dg, int rows, int cols,
            bool glu_interleave, cudaStream_t st);
 

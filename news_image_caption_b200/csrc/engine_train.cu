@@ -38,6 +38,7 @@ struct TrainWs {
   void *raw, *draw;                            // [N, 2d]
   void *dlogits;                               // [N, ldl]
   float* dW;                                   // fp32 scratch for weight-normed matrices / K-V / embedding grads
+  size_t dW_floats;
   float* attn_scr;                             // [B, H, T, D] fp32
   float* vecs;                                 // [L*2d] fp32 scratch (K/V bias rows)
   int *band_rows, *band_loc, *band_cnt, *band_head;
@@ -85,6 +86,7 @@ TrainWs carve_train(const tnt_decoder* D, int B, int T, const int* S, void* ws) 
   dw = std::max(dw, d * ns * d);
   dw = std::max(dw, L * 2 * d * max_kdim);
   w.dW = static_cast<float*>(take(dw * sizeof(float)));
+  w.dW_floats = dw;
   w.attn_scr = static_cast<float*>(take(N * d * sizeof(float)));
   w.vecs = static_cast<float*>(take(L * 2 * d * sizeof(float)));
   w.band_rows = static_cast<int*>(take(sizeof(int) * N * TNT_MAX_CLUSTERS));
@@ -344,7 +346,23 @@ int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, int s) {
   TNT_TRY(colsum(dkv, ldkv, S * B, 2 * d, nullptr, gb + d, c.dt, false, false, c.st));
   float* gi = c.grad(at + "in_proj_weight");
   float* dst = gi ? gi + static_cast<size_t>(d) * d : w.dW;
-  if (S * B > 0) {
+  // A long reduction (the article: S*B = 32768 rows) over only (2d/128) x (kd/256) output tiles leaves most SMs idle, and
+  // narrower tiles are L2->SM bound (128 x 128 tiles: 213 us = 46 % of the tensor peak).  The rows are split into G
+  // groups of one grouped launch -- wide tiles on every SM -- whose fp32 partials are summed afterwards.
+  int G = 1;
+  const int Kr = S * B;
+  if (Kr >= 8192 && c.dt == TNT_BF16) {
+    const long tiles = static_cast<long>((2 * d + 127) / 128) * ((kd + 255) / 256);
+    while (G < 8 && tiles * G * 4 < 3L * num_sms() && Kr % (2 * G) == 0 && Kr / (2 * G) >= 2048) G *= 2;
+    const size_t need = (static_cast<size_t>(G) + (gi ? 0 : 1)) * 2 * d * kd;
+    if (need > w.dW_floats || (static_cast<size_t>(2) * d * kd) % 4) G = 1;
+  }
+  if (G > 1) {
+    float* parts = w.dW + (gi ? 0 : static_cast<size_t>(2) * d * kd);
+    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, dkv, ldkv, ctx->memory[s], kd, parts, kd, 2 * d, kd, Kr / G, TNT_F32, nullptr, 0, nullptr, 0.f,
+                 nullptr, G, static_cast<long>(Kr / G) * ldkv, static_cast<long>(Kr / G) * kd, 0, static_cast<long>(2) * d * kd));
+    TNT_TRY(sum_partials(dst, parts, G, static_cast<long>(2) * d * kd, c.st));
+  } else if (S * B > 0) {
     TNT_TRY(gemm(c, TNT_TN, EPI_NONE, dkv, ldkv, ctx->memory[s], kd, dst, kd, 2 * d, kd, S * B, TNT_F32));
   } else {
     TNT_CUDA(cudaMemsetAsync(dst, 0, sizeof(float) * 2 * d * kd, c.st));

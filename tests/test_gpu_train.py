@@ -218,6 +218,38 @@ def test_train_step_gradients(name, dtype):
     assert worst[0][0] < gtol, '\n'.join('%.3e %s' % w for w in worst[:12])
 
 
+@pytest.mark.parametrize('art_dim', [1024, 128])
+def test_train_step_long_context_weight_gradients(art_dim):
+    """An article of S*B = 8192 rows (bf16): the K/V projection weight gradient splits its reduction into groups of one
+    grouped GEMM launch whose fp32 partials are summed (engine_train.cu kv_param_grads); both destinations -- separate
+    k/v_proj_weight (kdim != d) and the in_proj_weight rows [d, 3d) (kdim == d) -- against autograd through the oracle."""
+    from news_image_caption_b200 import DynamicConvDecoder, build
+    from news_image_caption_b200.decoder import random_state_dict
+    from oracle import synth
+    build.build()
+    d, H, V, cut = 128, 2, 300, [100, 200, 300]
+    sdim = {'article': art_dim}
+    sd0 = random_state_dict(d=d, heads=H, ffn=128, kernels=(3,), vocab=V, cutoffs=cut, source_dim=sdim, seed=5)
+    dec = DynamicConvDecoder(decoder_output_dim=d, decoder_attention_heads=H, decoder_ffn_embed_dim=128,
+                             decoder_kernel_size_list=[3], vocab_size=V, adaptive_softmax_cutoff=cut[:-1], source_dim=sdim,
+                             dtype=torch.bfloat16)
+    dec.load_reference_state_dict(sd0)
+    dec.enable_training()
+    B, T = 16, 4
+    prev, tgt, ctx = synth.make_batch(B, T, V, ('image', 'article'), seed=9, S_img=3, S_art=512, d_art=art_dim)
+    f = dict(config=dict(heads=H, cutoffs=cut, sources=['image', 'article']), state_dict=sd0, prev=prev, target=tgt, contexts=ctx)
+    scale = 0.5
+    loss_o, n_o, sd = oracle_grads(f, scale)
+    out = dec.train_step(prev.cuda(), tgt.cuda(), {k: v.cuda() for k, v in ctx.items()}, loss_scale=scale)
+    torch.cuda.synchronize()
+    assert int(out[1].item()) == n_o
+    assert abs(out[0].item() - loss_o.item()) < 2e-2 * abs(loss_o.item())
+    keys = [k for k, _ in dec.named_parameters() if 'context_attns.article' in k]
+    assert any('k_proj_weight' in k for k in keys) == (art_dim != d)
+    worst = sorted(((l2_err(p.grad, sd[k].grad), k) for k, p in dec.named_parameters() if k in keys), reverse=True)
+    assert worst[0][0] < 1e-1, '\n'.join('%.3e %s' % w for w in worst[:8])
+
+
 DROP_CFG = dict(dropout=0.1, input_dropout=0.1, weight_dropout=0.1, attention_dropout=0.1, relu_dropout=0.05)
 
 
