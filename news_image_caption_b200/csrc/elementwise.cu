@@ -393,7 +393,9 @@ extern "C" int tnt_layernorm_bwd(const tnt_layernorm_bwd_params* p, tnt_stream s
   const size_t smem = 2 * static_cast<size_t>(p->C) * 4;
   if (p->C <= 1024) {
     const size_t smem_s = static_cast<size_t>(kWarps) * 2 * p->C * 4;           // <= 64 KB
-    const int grid_s = std::min((p->rows + kWarps - 1) / kWarps, 4 * num_sms());
+    // every CTA ends with 2*C atomics onto dgamma / dbeta: few CTAs with several rows per warp beat one row per warp
+    static const int per_sm = [] { const char* e = getenv("TNT_LN_BWD_CTAS_PER_SM"); return e ? std::max(1, atoi(e)) : 4; }();
+    const int grid_s = std::min((p->rows + kWarps - 1) / kWarps, per_sm * num_sms());
     if (p->dtype == TNT_BF16) {
       TNT_CUDA(cudaFuncSetAttribute(layernorm_bwd_small_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
       layernorm_bwd_small_kernel<bf16><<<grid_s, kWarps * 32, smem_s, as_stream(stream)>>>(*p);
