@@ -237,4 +237,17 @@ __device__ __forceinline__ void tile_bits_row(const uint8_t* mask, long m_stride
   if (lane == 0) out[b] = (bits & 0xFFFFu) | (min(live, 0xFFFFu) << 16);
 }
 
+// one row-wise copy of the weight refresh (tnt_decoder_finalize): out[r] = (g ? g[r] / ||v[r]|| : 1) * v[r], r < rows;
+// optional GLU pair interleave of the output rows; fp32 output for vectors, the engine dtype for matrices
+struct FoldJob {
+  const float* v; const float* g; void* out;
+  int rows, cols, glu, out_f32;
+  int row0;                       // first warp-row of this job in the batched launch
+  bool operator==(const FoldJob& o) const {
+    return v == o.v && g == o.g && out == o.out && rows == o.rows && cols == o.cols && glu == o.glu && out_f32 == o.out_f32;
+  }
+};
+// all jobs in one launch (warp per row); `jobs` is a device array ordered by row0
+int wn_fold_batch(const FoldJob* jobs, int n_jobs, int total_rows, int dtype, cudaStream_t st);
+
 }  // namespace tnt

@@ -302,11 +302,7 @@ __device__ __forceinline__ float sumsq8(const float4 (&a)[8], float sq) {
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kWarps * 32) wn_fold_kernel(const float* v, const float* g, T* out, int rows,
-                                                              int cols, int glu) {
-  const int lane = threadIdx.x & 31;
-  const int row = blockIdx.x * kWarps + (threadIdx.x >> 5);
-  if (row >= rows) return;
+__device__ __forceinline__ void fold_row(const float* v, const float* g, T* out, int rows, int cols, int glu, int row, int lane) {
   const float* vr = v + static_cast<long>(row) * cols;
   const bool vec = (cols & 3) == 0 && dev_aligned16(v) && dev_aligned16(out);
   int orow = row;
@@ -347,6 +343,34 @@ __global__ void __launch_bounds__(kWarps * 32) wn_fold_kernel(const float* v, co
     scale = g[row] / sqrtf(warp_sum(sq));
   }
   for (int c = lane; c < cols; c += 32) o[c] = from_f<T>(vr[c] * scale);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kWarps * 32) wn_fold_kernel(const float* v, const float* g, T* out, int rows,
+                                                              int cols, int glu) {
+  const int row = blockIdx.x * kWarps + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  fold_row<T>(v, g, out, rows, cols, glu, row, threadIdx.x & 31);
+}
+
+// every job of the weight refresh in one launch: warp-row -> job by binary search over row0
+template <typename T>
+__global__ void __launch_bounds__(kWarps * 32) wn_fold_batch_kernel(const FoldJob* jobs, int n_jobs, int total_rows) {
+  __shared__ int s_row0[1024];                 // n_jobs <= 1024 (engine_load.cu kMaxFoldJobs)
+  for (int i = threadIdx.x; i < n_jobs; i += kWarps * 32) s_row0[i] = jobs[i].row0;
+  __syncthreads();
+  const int wr = blockIdx.x * kWarps + (threadIdx.x >> 5);
+  if (wr >= total_rows) return;
+  int lo = 0, hi = n_jobs - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (s_row0[mid] <= wr) lo = mid;
+    else hi = mid - 1;
+  }
+  const FoldJob j = jobs[lo];
+  const int row = wr - j.row0, lane = threadIdx.x & 31;
+  if (j.out_f32) fold_row<float>(j.v, j.g, static_cast<float*>(j.out), j.rows, j.cols, j.glu, row, lane);
+  else fold_row<T>(j.v, j.g, static_cast<T*>(j.out), j.rows, j.cols, j.glu, row, lane);
 }
 
 __global__ void glu_bias_kernel(const float* b, float* out, int n) {
@@ -439,6 +463,17 @@ extern "C" int tnt_wn_fold(const float* v, const float* g, void* w_out, int rows
   TNT_LAUNCHED();
   return TNT_OK;
 }
+
+namespace tnt {
+int wn_fold_batch(const FoldJob* jobs, int n_jobs, int total_rows, int dtype, cudaStream_t st) {
+  if (n_jobs == 0 || total_rows == 0) return TNT_OK;
+  const int grid = (total_rows + kWarps - 1) / kWarps;
+  if (dtype == TNT_BF16) wn_fold_batch_kernel<bf16><<<grid, kWarps * 32, 0, st>>>(jobs, n_jobs, total_rows);
+  else wn_fold_batch_kernel<float><<<grid, kWarps * 32, 0, st>>>(jobs, n_jobs, total_rows);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+}  // namespace tnt
 
 extern "C" int tnt_glu_interleave_bias(const float* b, float* b_out, int n, tnt_stream stream) {
   using namespace tnt;

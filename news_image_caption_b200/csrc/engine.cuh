@@ -53,6 +53,8 @@ struct tnt_decoder {
   tnt::AdaSoftmax ada;
   void* scratch_dd = nullptr;          // [d, d] fp32 (finalize only)
   void* emb_scratch = nullptr;             // largest band table in the engine dtype (finalize only)
+  tnt::FoldJob* fold_dev = nullptr;             // device copy of the finalize job list (one batched launch refreshes the weights)
+  std::vector<tnt::FoldJob> fold_host;          //   and the list it was built from
   void* emb_proj[TNT_MAX_CLUSTERS] = {};   // band projections [d, dim_i] in the engine dtype (training backward)
   int emb_dim[TNT_MAX_CLUSTERS] = {};
   std::vector<cudaEvent_t> stage_events;   // training: gradients of stage i are final (tnt_decoder_stream_wait_stage)

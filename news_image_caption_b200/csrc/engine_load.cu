@@ -31,6 +31,8 @@ struct Arena {
 };
 
 // lays out every prepared tensor; base == nullptr only measures
+constexpr int kMaxFoldJobs = 1024;
+
 size_t plan(tnt_decoder* D, char* base) {
   const tnt_decoder_config& c = D->cfg;
   const size_t E = D->esz(), d = c.d, ns = c.n_sources, L = c.n_layers;
@@ -80,6 +82,7 @@ size_t plan(tnt_decoder* D, char* base) {
     }
     D->emb_scratch = a.take(max_band * d * E);
   }
+  D->fold_dev = static_cast<FoldJob*>(a.take(sizeof(FoldJob) * kMaxFoldJobs));
   return a.off;
 }
 
@@ -87,6 +90,33 @@ struct Loader {
   tnt_decoder* D;
   cudaStream_t st;
   int err = TNT_OK;
+  // row-wise copies (matrix folds / casts and fp32 vectors) are queued and run as ONE launch (flush): the ~70 fold launches
+  // and ~130 small device copies of a refresh were 0.4 ms of every training step
+  std::vector<FoldJob> jobs;
+  int total_rows = 0;
+  void push(const float* v, const float* g, void* out, int rows, int cols, bool glu, bool out_f32) {
+    if (jobs.size() >= static_cast<size_t>(kMaxFoldJobs)) {        // cannot happen for <= 4 sources x 8 layers
+      chk(tnt_wn_fold(v, g, out, rows, cols, glu, out_f32 ? TNT_F32 : D->cfg.dtype, st));
+      return;
+    }
+    jobs.push_back(FoldJob{v, g, out, rows, cols, glu ? 1 : 0, out_f32 ? 1 : 0, total_rows});
+    total_rows += rows;
+  }
+  void flush() {
+    if (jobs.empty() || err != TNT_OK) return;
+    if (!(jobs == D->fold_host)) {         // first refresh (or re-bound pointers): upload the list
+      if (cudaMemcpyAsync(D->fold_dev, jobs.data(), sizeof(FoldJob) * jobs.size(), cudaMemcpyHostToDevice, st) != cudaSuccess ||
+          cudaStreamSynchronize(st) != cudaSuccess) {
+        set_error("decoder_finalize: uploading the refresh job list failed");
+        err = TNT_ERR_CUDA;
+        return;
+      }
+      D->fold_host = jobs;
+    }
+    chk(wn_fold_batch(D->fold_dev, static_cast<int>(jobs.size()), total_rows, D->cfg.dtype, st));
+    jobs.clear();
+    total_rows = 0;
+  }
 
   const RawTensor* find(const std::string& k) {
     auto it = D->raw.find(k);
@@ -116,10 +146,10 @@ struct Loader {
     const RawTensor* g = find(p + "weight_g");
     if (g) {
       const RawTensor* v = need(p + "weight_v", static_cast<int64_t>(rows) * cols);
-      if (v && need(p + "weight_g", rows)) chk(tnt_wn_fold(v->data, g->data, w, rows, cols, glu, D->cfg.dtype, st));
+      if (v && need(p + "weight_g", rows)) push(v->data, g->data, w, rows, cols, glu, false);
     } else {
       const RawTensor* v = need(p + "weight", static_cast<int64_t>(rows) * cols);
-      if (v) chk(tnt_wn_fold(v->data, nullptr, w, rows, cols, glu, D->cfg.dtype, st));
+      if (v) push(v->data, nullptr, w, rows, cols, glu, false);
     }
     if (b) {
       const RawTensor* bb = need(p + "bias", rows);
@@ -130,13 +160,14 @@ struct Loader {
     }
   }
   void matrix(const float* src, void* dst, int rows, int cols) {   // plain cast of a weight slice
+    push(src, nullptr, dst, rows, cols, false, false);
+  }
+  void matrix_now(const float* src, void* dst, int rows, int cols) {   // same, launched immediately (dst is reused right away)
     chk(tnt_wn_fold(src, nullptr, dst, rows, cols, 0, D->cfg.dtype, st));
   }
-  void vec(const float* src, float* dst, size_t n) {
-    if (cudaMemcpyAsync(dst, src, n * 4, cudaMemcpyDeviceToDevice, st) != cudaSuccess) {
-      if (err == TNT_OK) set_error("decoder_finalize: device copy failed");
-      err = TNT_ERR_CUDA;
-    }
+  void vec(const float* src, float* dst, size_t n) {               // fp32 vector copy; long ones as rows of 1024
+    if (n > 4096 && n % 1024 == 0) push(src, nullptr, dst, static_cast<int>(n / 1024), 1024, false, true);
+    else push(src, nullptr, dst, 1, static_cast<int>(n), false, true);
   }
   void vec_key(const std::string& k, float* dst, size_t n) {
     const RawTensor* t = need(k, n);
@@ -276,9 +307,9 @@ extern "C" int tnt_decoder_finalize(tnt_decoder* D, tnt_stream stream) {
           return TNT_ERR_ARG;
         }
         D->emb_dim[i] = dim_i;
-        L.matrix(prj->data, D->emb_proj[i], d, dim_i);
+        L.matrix_now(prj->data, D->emb_proj[i], d, dim_i);
         // table_i (engine dtype copy) . proj_i^T * sqrt(d): tcgen05 GEMM for the bf16 engine, fp32 SIMT for parity mode
-        L.matrix(tab->data, D->emb_scratch, n_i, dim_i);
+        L.matrix_now(tab->data, D->emb_scratch, n_i, dim_i);
         tnt_linear_params lp = {};
         lp.a = D->emb_scratch; lp.lda = dim_i; lp.w = D->emb_proj[i]; lp.ldw = dim_i;
         lp.c = static_cast<char*>(D->table) + static_cast<size_t>(lo) * d * D->esz(); lp.ldc = d;
@@ -317,6 +348,7 @@ extern "C" int tnt_decoder_finalize(tnt_decoder* D, tnt_stream stream) {
         L.matrix(p2->data, const_cast<void*>(D->ada.out_w[i]), n_i, d);
     }
   }
+  L.flush();
   if (L.err != TNT_OK) return L.err;
   TNT_CUDA(cudaGetLastError());
   // the raw (fp32 master) pointers are kept: the training backward reads weight_v / weight_g / the band tables
