@@ -31,7 +31,8 @@ WORKLOADS = {
     'gen': dict(B=256, sources=('image', 'article'), tag='2src', what='GREEDY generation 32 steps (incremental DynamicConv ring + cached K/V)'),
 }
 # dram bytes (read + write) of one article K/V GEMM launch from the ncu --set full capture in profiles/ (None until captured)
-TRAFFIC_KV_GEMM = 573.8e6   # profiles/r1_ncu_full_step_B64_pair.txt, id 11: 90.2 MB read + 483.6 MB written
+TRAFFIC_KV_GEMM = 576.0e6   # profiles/r1_ncu_full_final.txt (final build): 91.1 MB read + 484.9 MB written
+TRAFFIC_STEP_ATTN = 389.6e6  # same file, gen workload seed 1234: 385.4 MB read + 4.2 MB written per xattn_step_kernel launch
 WORKLOAD = 'tell-decoder-2src L4 d1024 H16 K3/7/15/31 V50265 fwd+adaptive-loss B64/gpu T32 S49+512'
 
 
@@ -342,7 +343,7 @@ def main():
         x_ms = xs_ms.value / max(xs_n.value, 1)
         ach = byts / (x_ms * 1e-3) / 1e9 if x_ms > 0 else 0.0
         roofline = {'bound': 'hbm', 'kernel': 'xattn_step_kernel: decode-step cross-attention over the cached image + article K/V of one layer (one launch)',
-                    'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': None,
+                    'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': TRAFFIC_STEP_ATTN,
                     'peak_source': which + ' hbm_gbs', 'bytes_per_launch': byts, 'ms_per_launch': x_ms,
                     'launches_timed': xs_n.value, 'live_keys_per_caption': live / B_PER_GPU, 'note': 'timed on the eager step 0 of every generate call (steps 1.. replay a CUDA graph)',
                     'kv_proj_gemm_tflops': achieved, 'kv_proj_ms': gemm_ms}

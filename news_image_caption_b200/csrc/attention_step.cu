@@ -7,7 +7,7 @@
 // in flight, not around tensor cores:
 //   CTA   = (caption b, group of 8 heads): the 8 heads' K (or V) values of one key are 1 KB contiguous in the
 //           cache [S, B, L*2d]; padded keys (key_padding_mask) are never fetched (exp(-inf) = 0 exactly).
-//   warp  = a strided subset of the keys; lane = (head = lane / 4, 16 of the 64 dims): scores by 2 shuffles,
+//   warp  = a strided subset of the keys; lane = (head = lane / 4, two 8-dim pieces of the 64 dims): scores by 2 shuffles,
 //           running (max, sum, acc[16]) per lane in fp32 (flash-decoding), kUnroll keys loaded before use.
 //   merge = the warps' partial (max, sum, acc) through shared memory; bf16 output, optional LSE.
 #include <algorithm>
@@ -72,7 +72,10 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(const __grid_co
   const tnt_xattn_params& p = batch.p[src];
   const int rem = item % per_src, slot = rem / n_hg, hg = rem - slot * n_hg;
   const int b = batch.order[src] ? batch.order[src][slot] : slot;      // long captions are started first (1.7 waves of CTAs)
-  const int h = hg * kHeadsPerCta + (lane >> 2), d0 = (lane & 3) * 16;
+  // lane q of a head's 4 lanes owns dims [8q, 8q+8) and [32+8q, 32+8q+8): each of its two 16-byte loads then fills whole
+  // 32-byte sectors together with its neighbours (dims [16q, 16q+16) made every sector cross L2->SM twice: ncu 770 MB per
+  // launch for 385 MB of DRAM reads)
+  const int h = hg * kHeadsPerCta + (lane >> 2), d0 = (lane & 3) * 8;
   const bf16* qp = reinterpret_cast<const bf16*>(p.q) + static_cast<long>(b) * p.q_stride_b + h * 64 + d0;
   const int bk = p.kv_group > 1 ? b / p.kv_group : b;     // beams of one caption share its K / V / mask
   const bf16* kp = reinterpret_cast<const bf16*>(p.k) + static_cast<long>(bk) * p.k_stride_b + h * 64 + d0;
@@ -83,7 +86,7 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(const __grid_co
 
   float q[16];
   {
-    const uint4 a = *reinterpret_cast<const uint4*>(qp), c = *reinterpret_cast<const uint4*>(qp + 8);
+    const uint4 a = *reinterpret_cast<const uint4*>(qp), c = *reinterpret_cast<const uint4*>(qp + 32);
     unpack16(a, c, q);
 #pragma unroll
     for (int i = 0; i < 16; ++i) q[i] *= p.scale * 1.4426950408889634f;     // scores in the log2 domain
@@ -121,9 +124,9 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(const __grid_co
         const bf16* kk = kp + ky * p.k_stride_s;
         const bf16* vv = vp + ky * p.v_stride_s;
         kr[u][0] = ldg_stream(kk);
-        kr[u][1] = ldg_stream(kk + 8);
+        kr[u][1] = ldg_stream(kk + 32);
         vr[u][0] = ldg_stream(vv);
-        vr[u][1] = ldg_stream(vv + 8);
+        vr[u][1] = ldg_stream(vv + 32);
       }
     }
 #pragma unroll
@@ -181,7 +184,7 @@ __global__ void __launch_bounds__(kWarps * 32) xattn_step_kernel(const __grid_co
       t1[i] = o[8 + i];
     }
     store8(op, t0);
-    store8(op + 8, t1);
+    store8(op + 32, t1);
     if (p.lse && (lane & 3) == 0)                        // natural-log LSE of the scaled, masked scores
       p.lse[static_cast<long>(b) * p.H + h] = Ls > 0.f ? (M + log2f(Ls)) * 0.6931471805599453f : INFINITY;
   }
