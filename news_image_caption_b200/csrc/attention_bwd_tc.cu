@@ -134,7 +134,9 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    {   // the whole warp walks the loops, ONE elected lane issues: operands stay in uniform registers (a single divergent
+        // lane paid an ELECT + 5 R2UR.BROADCAST + descriptor arithmetic in vector registers per tcgen05.mma / bulk copy)
+      const bool leader = ptx::elect_one();
       int ks = 0;
       uint32_t kph = 0, it = 0;
       for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
@@ -144,21 +146,21 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         const uint32_t live = ent >> 16;
         const int c0 = hp * 2 * D;
         ptx::mbar_wait(&bar->q_empty, (it & 1) ^ 1);
-        ptx::mbar_arrive_expect_tx(&bar->q_full, 2 * n_qt * QT_BYTES);
+        if (leader) ptx::mbar_arrive_expect_tx(&bar->q_full, 2 * n_qt * QT_BYTES);
         for (int j = 0; j < n_qt; ++j) {
           for (int h = 0; h < 2; ++h) {
-            ptx::tma_load_3d(sQ + j * QT_BYTES + h * TQ * 128, &tmQ, &bar->q_full, c0 + h * D, b, j * TQ);
-            ptx::tma_load_3d(sDO + j * QT_BYTES + h * TQ * 128, &tmDO, &bar->q_full, c0 + h * D, b, j * TQ);
+            if (leader) ptx::tma_load_3d(sQ + j * QT_BYTES + h * TQ * 128, &tmQ, &bar->q_full, c0 + h * D, b, j * TQ);
+            if (leader) ptx::tma_load_3d(sDO + j * QT_BYTES + h * TQ * 128, &tmDO, &bar->q_full, c0 + h * D, b, j * TQ);
           }
         }
         for (uint32_t m = live; m; m &= m - 1) {
           const int i = __ffs(m) - 1;
           ptx::mbar_wait(&bar->kv_empty[ks], kph ^ 1);
-          ptx::mbar_arrive_expect_tx(&bar->kv_full[ks], KV_STAGE);
+          if (leader) ptx::mbar_arrive_expect_tx(&bar->kv_full[ks], KV_STAGE);
           uint8_t* st = sKV + ks * KV_STAGE;
           for (int h = 0; h < 2; ++h) {
-            ptx::tma_load_3d(st + h * TKEYS * 128, &tmK, &bar->kv_full[ks], c0 + h * D, b, i * TKEYS);
-            ptx::tma_load_3d(st + KV_HALF + h * TKEYS * 128, &tmV, &bar->kv_full[ks], c0 + h * D, b, i * TKEYS);
+            if (leader) ptx::tma_load_3d(st + h * TKEYS * 128, &tmK, &bar->kv_full[ks], c0 + h * D, b, i * TKEYS);
+            if (leader) ptx::tma_load_3d(st + KV_HALF + h * TKEYS * 128, &tmV, &bar->kv_full[ks], c0 + h * D, b, i * TKEYS);
           }
           if (++ks == KVS) { ks = 0; kph ^= 1; }
         }
@@ -167,7 +169,9 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    {   // the whole warp walks the loops, ONE elected lane issues: operands stay in uniform registers (a single divergent
+        // lane paid an ELECT + 5 R2UR.BROADCAST + descriptor arithmetic in vector registers per tcgen05.mma / bulk copy)
+      const bool leader = ptx::elect_one();
       const uint32_t idesc_s = ptx::umma_idesc_bf16(128, TQ, 0, 0);       // K-major A (keys x d), K-major B (q x d)
       const uint32_t idesc_g = ptx::umma_idesc_bf16(128, D, 0, 1);        // K-major A (keys x q), MN-major B (q x d)
       const uint32_t idesc_q = ptx::umma_idesc_bf16(128, 2 * TQ, 1, 1);   // MN-major A (keys x (h,d)), MN-major B
@@ -180,13 +184,13 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int h = 0; h < 2; ++h) {
 #pragma unroll
           for (int k = 0; k < D / 16; ++k) {
-            ptx::umma_bf16_ss(tmem + COL_S + h * 32, ptx::umma_smem_desc(k_addr + h * TKEYS * 128 + k * 32, 16, 1024),
+            if (leader) ptx::umma_bf16_ss(tmem + COL_S + h * 32, ptx::umma_smem_desc(k_addr + h * TKEYS * 128 + k * 32, 16, 1024),
                               ptx::umma_smem_desc(q_addr + h * TQ * 128 + k * 32, 16, 1024), idesc_s, k != 0);
-            ptx::umma_bf16_ss(tmem + COL_DP + h * 32, ptx::umma_smem_desc(v_addr + h * TKEYS * 128 + k * 32, 16, 1024),
+            if (leader) ptx::umma_bf16_ss(tmem + COL_DP + h * 32, ptx::umma_smem_desc(v_addr + h * TKEYS * 128 + k * 32, 16, 1024),
                               ptx::umma_smem_desc(do_addr + h * TQ * 128 + k * 32, 16, 1024), idesc_s, k != 0);
           }
         }
-        ptx::umma_commit(&bar->s_ready);
+        if (leader) ptx::umma_commit(&bar->s_ready);
       };
       for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
         const int n_iter = __popc(slot_entry(wl, listed, item / HP, n_tiles) >> 16) * n_qt;    // i below counts LIVE key tiles
@@ -224,29 +228,29 @@ xattn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
             for (int k = 0; k < TQ / 16; ++k) {
               // A: K-steps 2h+k of the [keys x 64 (h,q)] tile; B: 16 query rows x 128 B of Q_h / dO_h (MN-major)
-              ptx::umma_bf16_ss(tmem + COL_DV + h * D, ptx::umma_smem_desc(p_addr + (2 * h + k) * 32, 16, 1024),
+              if (leader) ptx::umma_bf16_ss(tmem + COL_DV + h * D, ptx::umma_smem_desc(p_addr + (2 * h + k) * 32, 16, 1024),
                                 ptx::umma_smem_desc(do_addr + h * TQ * 128 + k * 2048, TQ * 128, 1024), idesc_g,
                                 (j | k) != 0);
-              ptx::umma_bf16_ss(tmem + COL_DK + h * D, ptx::umma_smem_desc(ds_addr + (2 * h + k) * 32, 16, 1024),
+              if (leader) ptx::umma_bf16_ss(tmem + COL_DK + h * D, ptx::umma_smem_desc(ds_addr + (2 * h + k) * 32, 16, 1024),
                                 ptx::umma_smem_desc(q_addr + h * TQ * 128 + k * 2048, TQ * 128, 1024), idesc_g,
                                 (j | k) != 0);
             }
           }
 #pragma unroll
           for (int k = 0; k < TKEYS / 16; ++k) {
-            ptx::umma_bf16_ss(tmem + COL_DQ + j * 64, ptx::umma_smem_desc(k_addr + k * 2048, TKEYS * 128, 1024),
+            if (leader) ptx::umma_bf16_ss(tmem + COL_DQ + j * 64, ptx::umma_smem_desc(k_addr + k * 2048, TKEYS * 128, 1024),
                               ptx::umma_smem_desc(ds_addr + k * 2048, 16, 1024), idesc_q, (i | k) != 0);
           }
-          ptx::umma_commit(&bar->p_empty);
+          if (leader) ptx::umma_commit(&bar->p_empty);
           if (j == n_qt - 1) {
-            ptx::umma_commit(&bar->acc_ready);
-            ptx::umma_commit(&bar->kv_empty[cur_ks]);
+            if (leader) ptx::umma_commit(&bar->acc_ready);
+            if (leader) ptx::umma_commit(&bar->kv_empty[cur_ks]);
             ++tile_glob;
             if (++ks == KVS) { ks = 0; kph ^= 1; }
           }
         }
-        ptx::umma_commit(&bar->dq_ready);
-        ptx::umma_commit(&bar->q_empty);
+        if (leader) ptx::umma_commit(&bar->dq_ready);
+        if (leader) ptx::umma_commit(&bar->q_empty);
       }
     }
     __syncwarp();

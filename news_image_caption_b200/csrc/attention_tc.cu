@@ -139,7 +139,9 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    {   // the whole warp walks the loops, ONE elected lane issues: operands stay in uniform registers (a single divergent
+        // lane paid an ELECT + 5 R2UR.BROADCAST + descriptor arithmetic in vector registers per tcgen05.mma / bulk copy)
+      const bool leader = ptx::elect_one();
       int ks = 0, vs = 0;
       uint32_t kph = 0, vph = 0, it = 0;
       for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
@@ -149,23 +151,23 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const uint32_t live = ent >> 16;
         const int c0 = hp * 2 * D;
         ptx::mbar_wait(&bar->q_empty, (it & 1) ^ 1);
-        ptx::mbar_arrive_expect_tx(&bar->q_full, Q_BYTES);
-        ptx::tma_load_3d(sQ, &tmQ, &bar->q_full, c0, b, qt * TQ);
-        ptx::tma_load_3d(sQ + TQ * 128, &tmQ, &bar->q_full, c0 + D, b, qt * TQ);
+        if (leader) ptx::mbar_arrive_expect_tx(&bar->q_full, Q_BYTES);
+        if (leader) ptx::tma_load_3d(sQ, &tmQ, &bar->q_full, c0, b, qt * TQ);
+        if (leader) ptx::tma_load_3d(sQ + TQ * 128, &tmQ, &bar->q_full, c0 + D, b, qt * TQ);
         for (uint32_t m = live; m; m &= m - 1) {
           const int i = __ffs(m) - 1;
           ptx::mbar_wait(&bar->k_empty[ks], kph ^ 1);
-          ptx::mbar_arrive_expect_tx(&bar->k_full[ks], KV_STAGE);
-          ptx::tma_load_3d(sK + ks * KV_STAGE, &tmK, &bar->k_full[ks], c0, b, i * TKEYS);
-          ptx::tma_load_3d(sK + ks * KV_STAGE + TKEYS * 128, &tmK, &bar->k_full[ks], c0 + D, b, i * TKEYS);
+          if (leader) ptx::mbar_arrive_expect_tx(&bar->k_full[ks], KV_STAGE);
+          if (leader) ptx::tma_load_3d(sK + ks * KV_STAGE, &tmK, &bar->k_full[ks], c0, b, i * TKEYS);
+          if (leader) ptx::tma_load_3d(sK + ks * KV_STAGE + TKEYS * 128, &tmK, &bar->k_full[ks], c0 + D, b, i * TKEYS);
           if (++ks == KS) { ks = 0; kph ^= 1; }
         }
         for (uint32_t m = live; m; m &= m - 1) {
           const int i = __ffs(m) - 1;
           ptx::mbar_wait(&bar->v_empty[vs], vph ^ 1);
-          ptx::mbar_arrive_expect_tx(&bar->v_full[vs], KV_STAGE);
-          ptx::tma_load_3d(sV + vs * KV_STAGE, &tmV, &bar->v_full[vs], c0, b, i * TKEYS);
-          ptx::tma_load_3d(sV + vs * KV_STAGE + TKEYS * 128, &tmV, &bar->v_full[vs], c0 + D, b, i * TKEYS);
+          if (leader) ptx::mbar_arrive_expect_tx(&bar->v_full[vs], KV_STAGE);
+          if (leader) ptx::tma_load_3d(sV + vs * KV_STAGE, &tmV, &bar->v_full[vs], c0, b, i * TKEYS);
+          if (leader) ptx::tma_load_3d(sV + vs * KV_STAGE + TKEYS * 128, &tmV, &bar->v_full[vs], c0 + D, b, i * TKEYS);
           if (++vs == VS) { vs = 0; vph ^= 1; }
         }
       }
@@ -173,7 +175,9 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    {   // the whole warp walks the loops, ONE elected lane issues: operands stay in uniform registers (a single divergent
+        // lane paid an ELECT + 5 R2UR.BROADCAST + descriptor arithmetic in vector registers per tcgen05.mma / bulk copy)
+      const bool leader = ptx::elect_one();
       const uint32_t idesc_qk = ptx::umma_idesc_bf16(128, TQ, 0, 0);
       const uint32_t idesc_pv = ptx::umma_idesc_bf16(128, 2 * TQ, 1, 1);
       int ks = 0, vs = 0, ps = 0;
@@ -195,14 +199,14 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             for (int k = 0; k < D / 16; ++k) {
               const uint64_t ad = ptx::umma_smem_desc(k_addr + h * TKEYS * 128 + k * 32, 16, 1024);
               const uint64_t bd = ptx::umma_smem_desc(q_addr + h * TQ * 128 + k * 32, 16, 1024);
-              ptx::umma_bf16_ss(tmem + i * 64 + h * 32, ad, bd, idesc_qk, k != 0);
+              if (leader) ptx::umma_bf16_ss(tmem + i * 64 + h * 32, ad, bd, idesc_qk, k != 0);
             }
           }
-          ptx::umma_commit(&bar->k_empty[ks]);
+          if (leader) ptx::umma_commit(&bar->k_empty[ks]);
           if (++ks == KS) { ks = 0; kph ^= 1; }
         }
-        ptx::umma_commit(&bar->q_empty);
-        ptx::umma_commit(&bar->s_ready);
+        if (leader) ptx::umma_commit(&bar->q_empty);
+        if (leader) ptx::umma_commit(&bar->s_ready);
         ptx::mbar_wait(&bar->o_empty, par ^ 1);            // previous item's output has been read
         ptx::tc_fence_after();
         for (int i = 0; i < nl; ++i) {
@@ -216,14 +220,14 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             // A = V^T: MN-major, two 64-channel atoms (the two heads) TKEYS*128 B apart, 8-key groups 1024 B apart
             const uint64_t ad = ptx::umma_smem_desc(v_addr + k * 2048, TKEYS * 128, 1024);
             const uint64_t bd = ptx::umma_smem_desc(p_addr + k * 2048, 16, 1024);
-            ptx::umma_bf16_ss(tmem + O_COL, ad, bd, idesc_pv, (i | k) != 0);
+            if (leader) ptx::umma_bf16_ss(tmem + O_COL, ad, bd, idesc_pv, (i | k) != 0);
           }
-          ptx::umma_commit(&bar->v_empty[vs]);
-          ptx::umma_commit(&bar->p_empty[ps]);
+          if (leader) ptx::umma_commit(&bar->v_empty[vs]);
+          if (leader) ptx::umma_commit(&bar->p_empty[ps]);
           if (++vs == VS) { vs = 0; vph ^= 1; }
           if (++ps == PS) { ps = 0; pph ^= 1; }
         }
-        ptx::umma_commit(&bar->o_ready);
+        if (leader) ptx::umma_commit(&bar->o_ready);
       }
     }
     __syncwarp();

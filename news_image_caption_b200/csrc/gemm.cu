@@ -20,6 +20,8 @@ constexpr int kThreads = 192;             // warp 0: TMA producer, warp 1: MMA i
 constexpr int A_STAGE_BYTES = BM * BK * 2;
 constexpr uint32_t kTmemCols = 512;       // 2 accumulator stages x 256 fp32 columns
 constexpr int kAccStride = 256;
+// interleaved accumulators of a single-CTA tile: nacc * BN <= kAccStride columns per accumulator stage
+inline int acc_count(int cg, int bn) { return cg != 1 ? 1 : bn <= 64 ? 4 : bn <= 128 ? 2 : 1; }
 constexpr int kMaxStages = 8;
 constexpr int kSmemBudget = 220 * 1024;
 
@@ -104,8 +106,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int num_kb = (Kred + BK - 1) / BK;
 
   if (warp == 0) {
-    // ------------------------------------------------------------ TMA producer (every CTA)
-    if (lane == 0) {
+    // ------------------------------------------------------------ TMA producer (warp 0 of every CTA)
+    // the whole warp walks the loop, one elected lane issues (uniform registers for the descriptors / coordinates; a
+    // single divergent lane paid an ELECT + 5 R2UR.BROADCAST per bulk copy)
+    {
+      const bool leader = ptx::elect_one();
       int s = 0;
       uint32_t ph = 0;
       for (int tile = worker; tile < total_tiles; tile += n_workers) {
@@ -115,6 +120,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int m0 = mt * BMT + rank * BM, n0 = nt * BN + rank * BNL;
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(&empty[s], ph ^ 1);
+          if (leader) {
           uint8_t* sa = smem + s * stage_bytes;
           if (CG == 1) {
             ptx::mbar_arrive_expect_tx(&full[s], stage_bytes);
@@ -147,15 +153,32 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 ptx::tma_load_3d_pair(sa + A_STAGE_BYTES + at * 8192, &tmW, fb, n0 + at * 64, kb * BK, gw);
             }
           }
+          }
+          __syncwarp();
           if (++s == stages) { s = 0; ph ^= 1; }
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer (one thread of the leader CTA)
-    if (lane == 0 && rank == 0) {
+    // ------------------------------------------------------------ MMA issuer (warp 1 of the leader CTA)
+    // The WHOLE warp walks the loop and one elected lane issues: with a single divergent lane every descriptor lived in
+    // vector registers and each tcgen05.mma cost an ELECT + 5 R2UR.BROADCAST + ~25 predicated descriptor instructions
+    // -- ~150 SASS instructions = 660 cycles per k-block, which (not the tensor pipe, not TMA) bounded every k-loop
+    // (ncu source view: the producer spins on `empty`, the issuer never waits on `full`).  Warp-uniform code keeps the
+    // descriptors in uniform registers; they are built once and advanced by adding to their 14-bit address field.
+    if (rank == 0) {
+      const bool leader = ptx::elect_one();
       const uint32_t idesc = ptx::umma_idesc_bf16(BMT, BN, g.a_mn, g.b_mn);
+      // K-major: 32 bytes per K step inside the 128-byte row; MN-major: 16 k-rows x 128 B per step,
+      // 64-element atoms 8192 B apart (LBO), 8-row groups 1024 B apart (SBO)
+      const uint32_t smem0 = ptx::smem_u32(smem);
+      const uint64_t adesc0 = g.a_mn ? ptx::umma_smem_desc(smem0, 8192, 1024) : ptx::umma_smem_desc(smem0, 16, 1024);
+      const uint64_t bdesc0 = g.b_mn ? ptx::umma_smem_desc(smem0 + A_STAGE_BYTES, 8192, 1024)
+                                     : ptx::umma_smem_desc(smem0 + A_STAGE_BYTES, 16, 1024);
+      const uint32_t ka = (g.a_mn ? 2048u : UMMA_K * 2u) >> 4, kbs = (g.b_mn ? 2048u : UMMA_K * 2u) >> 4;   // per K step
+      const uint32_t stage_step = static_cast<uint32_t>(stage_bytes) >> 4;
+      const int nacc = CG == 1 ? g.nacc : 1;
       int s = 0, it = 0;
       uint32_t ph = 0;
       for (int tile = worker; tile < total_tiles; tile += n_workers, ++it) {
@@ -167,36 +190,38 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kb = 0; kb < num_kb; ++kb) {
           ptx::mbar_wait(&full[s], ph);                // TMA bytes have landed (in both CTAs)
           ptx::tc_fence_after();
-          const uint32_t a_addr = ptx::smem_u32(smem + s * stage_bytes);
-          const uint32_t b_addr = a_addr + A_STAGE_BYTES;
+          if (leader) {
+            const uint64_t ad = adesc0 + static_cast<uint64_t>(s * stage_step);
+            const uint64_t bd = bdesc0 + static_cast<uint64_t>(s * stage_step);
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            // K-major: 32 bytes per K step inside the 128-byte row; MN-major: 16 k-rows x 128 B per step,
-            // 64-element atoms 8192 B apart (LBO), 8-row groups 1024 B apart (SBO)
-            const uint64_t ad = g.a_mn ? ptx::umma_smem_desc(a_addr + k * 2048, 8192, 1024)
-                                       : ptx::umma_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
-            const uint64_t bd = g.b_mn ? ptx::umma_smem_desc(b_addr + k * 2048, 8192, 1024)
-                                       : ptx::umma_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
-            if (CG == 2) ptx::umma_bf16_ss_pair(d_tmem, ad, bd, idesc, (kb | k) != 0);
-            else ptx::umma_bf16_ss(d_tmem, ad, bd, idesc, (kb | k) != 0);
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              if (CG == 2) ptx::umma_bf16_ss_pair(d_tmem, ad + k * ka, bd + k * kbs, idesc, (kb | k) != 0);
+              // narrow single-CTA tiles rotate over `nacc` accumulators BN columns apart; the epilogue adds them
+              else ptx::umma_bf16_ss(d_tmem + (k & (nacc - 1)) * BN, ad + k * ka, bd + k * kbs, idesc, kb != 0 || k >= nacc);
+            }
+            if (CG == 2) ptx::umma_commit_pair(&empty[s]);   // frees the smem slot of both CTAs when these MMAs retire
+            else ptx::umma_commit(&empty[s]);
           }
-          if (CG == 2) ptx::umma_commit_pair(&empty[s]);   // frees the smem slot of both CTAs when these MMAs retire
-          else ptx::umma_commit(&empty[s]);
+          __syncwarp();
           if (++s == stages) { s = 0; ph ^= 1; }
         }
-        if (num_kb > 0) {                              // accumulator complete -> epilogue (of both CTAs)
-          if (CG == 2) ptx::umma_commit_pair(&tfull[as]);
-          else ptx::umma_commit(&tfull[as]);
-        } else {                                       // empty reduction: the epilogue writes zeros
-          ptx::mbar_arrive(&tfull[as]);
-          if (CG == 2) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tfull[as]), 1));
+        if (leader) {
+          if (num_kb > 0) {                            // accumulator complete -> epilogue (of both CTAs)
+            if (CG == 2) ptx::umma_commit_pair(&tfull[as]);
+            else ptx::umma_commit(&tfull[as]);
+          } else {                                     // empty reduction: the epilogue writes zeros
+            ptx::mbar_arrive(&tfull[as]);
+            if (CG == 2) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&tfull[as]), 1));
+          }
         }
+        __syncwarp();
       }
     }
     __syncwarp();
   } else {
     // ------------------------------------------------------------ epilogue warps (TMEM -> regs -> HBM)
     const int q = warp & 3;                            // TMEM lane quadrant this warp may read
+    const int nacc_e = CG == 1 ? g.nacc : 1;
     int it = 0;
     for (int tile = worker; tile < total_tiles; tile += n_workers, ++it) {
       int mt, nt, grp;
@@ -227,6 +252,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint32_t v[32];
         ptx::tmem_ld_32x32(taddr + c * 32, v);
         ptx::tmem_ld_wait();
+        for (int j = 1; j < nacc_e; ++j) {               // the other accumulators of a narrow tile (see the MMA issuer)
+          uint32_t u[32];
+          ptx::tmem_ld_32x32(taddr + j * BN + c * 32, u);
+          ptx::tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(u[i]));
+        }
         if (EPI != EPI_LSE && EPI != EPI_GLU && g.m_dyn && !g.a_mn && row >= M && row < g.M) {
           // pad rows of a dynamic-M problem get zeros: a later TN GEMM reduces over whole 64-row blocks
           zero_store<TOut, 32>(g, grp, row, n0);
@@ -433,6 +465,8 @@ int make_tmap_bf16_3d(CUtensorMap* tm, const void* base, long d0, long d1, long 
 
 static int g_cta_group = 0;   // test hook: 0 = automatic, 1 / 2 = force the single-CTA / CTA-pair kernel
 static int g_force_stages = 0;   // tuning hook: cap the smem ring depth
+static int g_single_acc = 1;  // tuning hook: 0 = narrow tiles rotate their MMAs over 2-4 TMEM accumulators (measured: no gain --
+                              // the k-loop was bound by the issuing thread's instruction stream, not by accumulator dependencies)
 static int g_force_bn = 0;    // tuning hook: force the tile width (32..256; CTA pair: 64..256)
 
 // tile shape the tcgen05 dispatcher uses: CTA-pair 256 x 256 tiles when the problem fills the 74 SM pairs for
@@ -499,7 +533,9 @@ static int launch_tc_cg(const GemmArgs& g, int BN, cudaStream_t st) {
     TNT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBudget + 4096));
     attr_set = true;
   }
-  TNT_CUDA(launch_pdl(kern, dim3(grid), dim3(tc::kThreads), smem, st, CG, tmA, tmW, g, BN, stages, n_tiles));
+  GemmArgs ga = g;
+  ga.nacc = g_single_acc ? 1 : tc::acc_count(CG, BN);
+  TNT_CUDA(launch_pdl(kern, dim3(grid), dim3(tc::kThreads), smem, st, CG, tmA, tmW, ga, BN, stages, n_tiles));
   TNT_LAUNCHED();
   return TNT_OK;
 }
@@ -622,4 +658,5 @@ extern "C" int tnt_linear_fwd(const tnt_linear_params* p, tnt_stream stream) {
 extern "C" void tnt_debug_force_simt_gemm(int on) { tnt::gemm_force_simt(on != 0); }
 extern "C" void tnt_debug_gemm_cta_group(int cg) { tnt::g_cta_group = (cg == 1 || cg == 2) ? cg : 0; }
 extern "C" void tnt_debug_gemm_stages(int n) { tnt::g_force_stages = n > 0 ? n : 0; }
+extern "C" void tnt_debug_gemm_single_acc(int on) { tnt::g_single_acc = on ? 1 : 0; }
 extern "C" void tnt_debug_gemm_tile_n(int bn) { tnt::g_force_bn = (bn == 32 || bn == 64 || bn == 128 || bn == 256) ? bn : 0; }

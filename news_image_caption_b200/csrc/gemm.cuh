@@ -14,6 +14,7 @@ struct GemmArgs {
   int groups;
   long sa, sw, sbias, sres, sc;
   int vec_ok;               // C (and residual) rows allow 16-byte vector access
+  int nacc;                 // tcgen05 single-CTA tiles: interleaved TMEM accumulators (1, 2 or 4; set by the launcher)
   // EPI_LSE only
   const int* target;        // [M] cluster-local target column or < 0
   float4* partials;         // [M, n_tiles] (max, sumexp, argmax bits, target logit or 0)

@@ -83,36 +83,45 @@ gemm_splitk_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   const int kb0 = min(num_kb, rank * per), kb1 = min(num_kb, kb0 + per);
   const int nk = kb1 - kb0;
 
+  // producer and issuer: the whole warp walks the loop, one elected lane issues (descriptors and coordinates stay in
+  // uniform registers; see gemm.cu)
   if (warp == 0) {
-    if (lane == 0) {
-      int s = 0;
-      uint32_t ph = 0;
-      for (int kb = kb0; kb < kb1; ++kb) {
-        ptx::mbar_wait(&empty[s], ph ^ 1);
+    const bool leader = ptx::elect_one();
+    int s = 0;
+    uint32_t ph = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      ptx::mbar_wait(&empty[s], ph ^ 1);
+      if (leader) {
         uint8_t* sa = ring + s * stage_bytes;
         ptx::mbar_arrive_expect_tx(&full[s], stage_bytes);
         ptx::tma_load_3d(sa, &tmA, &full[s], kb * BK, mt * BM, 0);
         ptx::tma_load_3d(sa + A_STAGE_BYTES, &tmW, &full[s], kb * BK, nt * BN, 0);
-        if (++s == stages) { s = 0; ph ^= 1; }
       }
+      __syncwarp();
+      if (++s == stages) { s = 0; ph ^= 1; }
     }
-    __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = ptx::umma_idesc_bf16(BM, BN, 0, 0);
-      int s = 0;
-      uint32_t ph = 0;
-      for (int i = 0; i < nk; ++i) {
-        ptx::mbar_wait(&full[s], ph);
-        ptx::tc_fence_after();
-        const uint32_t a_addr = ptx::smem_u32(ring + s * stage_bytes), b_addr = a_addr + A_STAGE_BYTES;
+    const bool leader = ptx::elect_one();
+    const uint32_t idesc = ptx::umma_idesc_bf16(BM, BN, 0, 0);
+    const uint32_t ring0 = ptx::smem_u32(ring);
+    const uint64_t adesc0 = ptx::umma_smem_desc(ring0, 16, 1024), bdesc0 = ptx::umma_smem_desc(ring0 + A_STAGE_BYTES, 16, 1024);
+    const uint32_t stage_step = static_cast<uint32_t>(stage_bytes) >> 4;
+    int s = 0;
+    uint32_t ph = 0;
+    for (int i = 0; i < nk; ++i) {
+      ptx::mbar_wait(&full[s], ph);
+      ptx::tc_fence_after();
+      if (leader) {
+        const uint64_t ad = adesc0 + static_cast<uint64_t>(s * stage_step), bd = bdesc0 + static_cast<uint64_t>(s * stage_step);
 #pragma unroll
         for (int k = 0; k < BK / UMMA_K; ++k)
-          ptx::umma_bf16_ss(tmem_base, ptx::umma_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024),
-                            ptx::umma_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024), idesc, (i | k) != 0);
+          ptx::umma_bf16_ss(tmem_base, ad + k * ((UMMA_K * 2) >> 4), bd + k * ((UMMA_K * 2) >> 4), idesc, (i | k) != 0);
         ptx::umma_commit(&empty[s]);
-        if (++s == stages) { s = 0; ph ^= 1; }
       }
+      __syncwarp();
+      if (++s == stages) { s = 0; ph ^= 1; }
+    }
+    if (leader) {
       if (nk > 0) ptx::umma_commit(tfull);
       else ptx::mbar_arrive(tfull);
     }
