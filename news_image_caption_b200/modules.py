@@ -232,6 +232,47 @@ class MultiHeadAttention(nn.Module):
         return          # static K/V: nothing is cached per beam
 
 
+def multi_head_attention_score_forward(query, key, embed_dim_to_check, num_heads, in_proj_weight, in_proj_bias, bias_k,
+                                       add_zero_attn, dropout_p, out_proj_weight=None, out_proj_bias=None, training=True,
+                                       key_padding_mask=None, attn_mask=None, use_separate_proj_weight=False,
+                                       q_proj_weight=None, k_proj_weight=None, static_k=None):
+    """multi_head.py:14-204 -- the copy-attention score head the pointer decoders import: head-averaged attention
+    probabilities [B,T,S(+1 bias_k row)(+1 zero row)] of query [T,B,E] over key [S,B,E]; no values, no output
+    projection (out_proj_* are accepted and unused, as in the reference).  Same argument order and meaning.
+    Forward only: the weights come from the attention kernel's head-averaging epilogue (its value operand is the
+    key tile, the attended output is discarded).  attn_mask / static_k are not used by any caller and raise."""
+    if attn_mask is not None or static_k is not None:
+        raise NotImplementedError('multi_head_attention_score_forward: attn_mask / static_k are not implemented')
+    T, B, E = query.shape
+    assert E == embed_dim_to_check                                              # :81
+    assert (E // num_heads) * num_heads == E, 'embed_dim must be divisible by num_heads'      # :85
+    if use_separate_proj_weight:
+        wq, wk = q_proj_weight, k_proj_weight
+        assert tuple(wq.shape) == (E, query.size(-1)) and tuple(wk.shape) == (E, key.size(-1))   # :113-118
+    else:
+        wq, wk = in_proj_weight[:E], in_proj_weight[E:2 * E]                      # :96-110 (q | k halves)
+    bq = bk = None
+    if in_proj_bias is not None:
+        bq, bk = in_proj_bias[:E], in_proj_bias[E:2 * E]
+    S = key.shape[0]
+    if key_padding_mask is not None:
+        assert key_padding_mask.size(0) == B and key_padding_mask.size(1) == S    # :161-163
+    with torch.no_grad():
+        q = linear(query, wq, bq)
+        k = linear(key, wk, bk)
+        rows = [k]
+        if bias_k is not None:
+            rows.append(bias_k.to(k.dtype).expand(1, B, E))                     # :130-135
+        if add_zero_attn:
+            rows.append(k.new_zeros(1, B, E))                                   # :165-168
+        if len(rows) > 1:
+            k = torch.cat(rows, 0)
+        drop = (dropout_p, _draw_seed(), 0) if training and dropout_p > 0 else None      # :199
+        _, w = ops.xattn(q, k, k, num_heads, (E // num_heads) ** -0.5, pad_mask=key_padding_mask,
+                         mask_S=S if key_padding_mask is not None else 0, need_weights=True, drop=drop)
+    return w
+
+
 class AdaptiveSoftmax(nn.Module):
     """softmax.py:43-222 (Grave et al.): head over cutoff[0] + n_tails classes, tail i = Linear(d, d / factor^(i+1),
     no bias) -> dropout -> Linear(., band size, no bias).  forward(X, target) -> (logit list, target list) exactly as

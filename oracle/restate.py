@@ -190,6 +190,32 @@ def mha(query, mem, pad_mask, sd: SD, p: str, H: int):
     return mha_attend(query, k, v, pad_mask, sd, p, H)
 
 
+def mha_score(query, key, wq, wk, bq, bk, bias_k, add_zero_attn: bool, pad_mask, H: int, prob_drop=None):
+    """`multi_head_attention_score_forward` (multi_head.py:14-204): the head-averaged attention
+    probabilities only -- no values, no output projection.  q = (Wq x + bq) d^-1/2 (:128),
+    k = [Wk m + bk ; bias_k ; 0] (:130-148, 165-168), key padding -> -inf on the memory rows only (:187-194),
+    softmax (:197), dropout (:199), sum over heads / H (:203-204).  query [T,B,E], key [S,B,E] -> [B,T,S(+1)(+1)]"""
+    T, B, E = query.shape
+    D = E // H
+    q = F.linear(query, wq, bq) * (D ** -0.5)
+    k = F.linear(key, wk, bk)
+    if bias_k is not None:
+        k = torch.cat([k, bias_k.expand(1, B, E)], 0)
+    if add_zero_attn:
+        k = torch.cat([k, k.new_zeros(1, B, E)], 0)
+    S2 = k.shape[0]
+    qh = q.reshape(T, B, H, D).permute(1, 2, 0, 3)
+    kh = k.reshape(S2, B, H, D).permute(1, 2, 0, 3)
+    s = qh @ kh.transpose(-1, -2)                            # [B,H,T,S2]
+    if pad_mask is not None:
+        full = torch.cat([pad_mask, pad_mask.new_zeros(B, S2 - pad_mask.shape[1])], 1)   # extra keys never masked
+        s = s.masked_fill(full[:, None, None, :], float('-inf'))
+    pr = torch.softmax(s, -1)
+    if prob_drop is not None:
+        pr = prob_drop(pr)
+    return pr.sum(1) / H
+
+
 # ----------------------------------------------------------------------------- decoder layer
 def decoder_layer(X: torch.Tensor, contexts: dict, sd: SD, p: str, H: int, K: int,
                   sources: Sequence[str], conv_hist: Optional[list] = None, kv_cache=None,

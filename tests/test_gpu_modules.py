@@ -150,3 +150,32 @@ def test_gehring_linear_and_adaptive_softmax_modules(M):
     lo, _ = O.adaptive_nll(X, tgt, sdo, [100, 200, 300])
     assert abs(loss.item() - lo.item()) < 1e-4 * abs(lo.item())
     assert rel_err(ada.get_log_prob(X.cuda()), O.adaptive_log_prob(X, sdo, [100, 200, 300])) < 1e-4
+
+
+@pytest.mark.parametrize('separate,bias_row,zero_row', [(False, True, True), (True, True, False), (False, False, False)])
+@pytest.mark.parametrize('dtype,tol', [(torch.float32, 1e-4), (torch.bfloat16, 2e-2)])
+def test_attention_score_forward(M, separate, bias_row, zero_row, dtype, tol):
+    """multi_head_attention_score_forward (multi_head.py:14-204): head-averaged copy-attention weights only."""
+    g = torch.Generator().manual_seed(31)
+    T, B, E, H, S = 7, 3, 128, 4, 45
+    q = torch.randn(T, B, E, generator=g)
+    mem = torch.randn(S, B, E, generator=g)
+    w = torch.randn(2 * E, E, generator=g) * 0.1
+    b = torch.randn(2 * E, generator=g) * 0.1
+    bias_k = torch.randn(1, 1, E, generator=g) if bias_row else None
+    pad = torch.rand(B, S, generator=g) > 0.6
+    pad[:, 0] = False
+    if bias_row:
+        pad[1] = True                                             # fully masked memory: only the extra keys remain
+    ref = O.mha_score(q, mem, w[:E], w[E:], b[:E], b[E:], bias_k, zero_row, pad, H)
+    wc = w.cuda()
+    kw = dict(use_separate_proj_weight=True, q_proj_weight=wc[:E], k_proj_weight=wc[E:]) if separate else {}
+    got = M.multi_head_attention_score_forward(q.cuda().to(dtype), mem.cuda().to(dtype), E, H, None if separate else wc, b.cuda(),
+                                               None if bias_k is None else bias_k.cuda(), zero_row, 0.0, None, None,
+                                               training=False, key_padding_mask=pad.cuda(), **kw)
+    assert got.shape == ref.shape
+    assert rel_err(got, ref) < tol
+    assert torch.allclose(got.float().sum(-1).cpu(), torch.ones(B, T), atol=1e-3)
+    with pytest.raises(NotImplementedError):
+        M.multi_head_attention_score_forward(q.cuda(), mem.cuda(), E, H, wc, b.cuda(), None, False, 0.0,
+                                             attn_mask=torch.zeros(T, S).cuda())

@@ -369,3 +369,28 @@ def test_pointer_greedy_generation_matches_reference():
     assert ids_r.shape == ids_o.shape and torch.equal(ids_r, ids_o)
     close(lp_o, lp_r)
     torch.set_grad_enabled(True)
+
+
+@pytest.mark.parametrize('separate,bias_row,zero_row', [(False, True, True), (True, True, False), (False, False, False)])
+def test_attention_score_forward_matches_reference(separate, bias_row, zero_row):
+    """oracle `mha_score` against the unmodified `multi_head_attention_score_forward` (multi_head.py:14-204)."""
+    import importlib
+    ri.load_tell()
+    mh = importlib.import_module('tell.modules.attention.multi_head')
+    g = torch.Generator().manual_seed(31)
+    T, B, E, H, S = 5, 3, 64, 4, 11
+    q = torch.randn(T, B, E, generator=g)
+    mem = torch.randn(S, B, E, generator=g)
+    w = torch.randn(2 * E, E, generator=g) * 0.1
+    b = torch.randn(2 * E, generator=g) * 0.1
+    bias_k = torch.randn(1, 1, E, generator=g) if bias_row else None
+    pad = torch.rand(B, S, generator=g) > 0.6
+    pad[:, 0] = False
+    kw = dict(use_separate_proj_weight=True, q_proj_weight=w[:E], k_proj_weight=w[E:]) if separate else {}
+    ref = mh.multi_head_attention_score_forward(q, mem, E, H, None if separate else w, b, bias_k, zero_row, 0.0, None, None,
+                                                training=False, key_padding_mask=pad, **kw)
+    got = O.mha_score(q, mem, w[:E], w[E:], b[:E], b[E:], bias_k, zero_row, pad, H)
+    assert ref.shape == (B, T, S + int(bias_row) + int(zero_row))
+    close(got, ref, 1e-6)
+    ref_self = mh.multi_head_attention_score_forward(q, q, E, H, w, b, bias_k, zero_row, 0.0, None, None, training=False)
+    close(O.mha_score(q, q, w[:E], w[E:], b[:E], b[E:], bias_k, zero_row, None, H), ref_self, 1e-6)   # qk_same branch (:92-95)
