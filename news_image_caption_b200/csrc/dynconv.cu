@@ -195,6 +195,48 @@ __device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+// NJ = taps per thread (two threads per (t, head) row; K <= 2 * NJ - 1 ... 2 * NJ)
+template <int NJ>
+__device__ __forceinline__ void band_softmax(const tnt_dynconv_params& p, const DropSpec& dr, const bf16* lraw, uint8_t* As,
+                                             int AS, int HK, int TTl, int t0, int b, int h0) {
+  const int K = p.K, B = p.B;
+  // a warp covers 16 consecutive timesteps of ONE head (head-major: the 4 heads' band rows sit 32 * AS bytes apart,
+  // a multiple of 128, so a timestep-major warp stored 4-way bank-conflicted); the thread's <= 17 taps stay in
+  // registers between the max, the sum and the store (the three-pass form re-read and re-exponentiated them: the
+  // kernel was bound by instruction issue, 64 % active, with half of its instructions in this block)
+  const int i = threadIdx.x >> 1, half = threadIdx.x & 1;          // TT * HG = 128 (t, head) rows, two threads each
+  const int hl = i / TT, t_raw = i - hl * TT;
+  const bool on = t_raw < TTl;                                       // rows beyond the tile: compute on row 0, write nothing
+  const int t = on ? t_raw : 0;
+  const bf16* l = lraw + t * HK + hl * K;
+  float e[NJ];
+  float m = -INFINITY;
+#pragma unroll
+  for (int jj = 0; jj < NJ; ++jj) {
+    const int j = half + 2 * jj;
+    e[jj] = j < K ? __bfloat162float(l[j]) : -INFINITY;
+    m = fmaxf(m, e[jj]);
+  }
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+  float sum = 0.f;
+#pragma unroll
+  for (int jj = 0; jj < NJ; ++jj) {
+    e[jj] = half + 2 * jj < K ? __expf(e[jj] - m) : 0.f;
+    sum += e[jj];
+  }
+  sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+  const float inv = 1.f / sum;
+  bf16* arow = reinterpret_cast<bf16*>(As + (hl * TT + t) * AS) + t;
+  const unsigned long long i0 = ((static_cast<unsigned long long>(t0 + t) * B + b) * p.H + h0 + hl) * K;
+#pragma unroll
+  for (int jj = 0; jj < NJ; ++jj) {
+    const int j = half + 2 * jj;
+    float w = e[jj] * inv;
+    if (dr.thr && j < K) w = drop_val(dr, i0 + j, w);
+    if (on && j < K) arow[j] = __float2bfloat16_rn(w);
+  }
+}
+
 // All global reads of the CTA (window rows, raw tap logits) are issued as cp.async up front: the earlier version's
 // staging loops (load -> store per iteration) serialised one memory latency per iteration and per thread, which --
 // not the arithmetic -- was what kept the kernel at 15 % of the HBM roofline.
@@ -228,9 +270,17 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_tc_kernel(tnt_dynconv_pa
   }
   {
     const int wpr = HK >> 1;                             // 4-byte words per timestep
-    for (int i = threadIdx.x; i < TTl * wpr; i += kThreads) {
-      const int r = i / wpr, wd = i - r * wpr;
-      cp_async4(lraw_s + (r * HK + 2 * wd) * 2, lg + (static_cast<long>(t0 + r) * B + b) * p.ldl + h0 * K + 2 * wd);
+    const int w0 = threadIdx.x >> 5, l0 = threadIdx.x & 31;          // warp = timestep row, lane = word: no division by K
+    if (wpr > 16) {
+      for (int r = w0; r < TTl; r += kThreads / 32) {
+        const bf16* src = lg + (static_cast<long>(t0 + r) * B + b) * p.ldl + h0 * K;
+        for (int wd = l0; wd < wpr; wd += 32) cp_async4(lraw_s + (r * HK + 2 * wd) * 2, src + 2 * wd);
+      }
+    } else {                                             // few taps: a row would leave most of a warp idle
+      for (int i = threadIdx.x; i < TTl * wpr; i += kThreads) {
+        const int r = i / wpr, wd = i - r * wpr;
+        cp_async4(lraw_s + (r * HK + 2 * wd) * 2, lg + (static_cast<long>(t0 + r) * B + b) * p.ldl + h0 * K + 2 * wd);
+      }
     }
   }
   for (int i = threadIdx.x; i < (HG * TT * AS) / 16; i += kThreads) reinterpret_cast<uint4*>(As)[i] = make_uint4(0, 0, 0, 0);
@@ -238,29 +288,11 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_tc_kernel(tnt_dynconv_pa
   __syncthreads();
   // soft-max of the K taps of every (t, head) and its row of the band matrix: A[hl][t][t + j] = w_j (window row c holds
   // time t0 - (K-1) + c, so output t reads rows t .. t+K-1); two threads per (t, head) would not pay: 128 x K exps
-  {
-    const int i = threadIdx.x >> 1, half = threadIdx.x & 1;          // TT * HG = 128 (t, head) rows, two threads each
-    const int t_raw = i / HG, hl = i - t_raw * HG;
-    const bool on = t_raw < TTl;                                       // rows beyond the tile: compute on row 0, write nothing
-    const int t = on ? t_raw : 0;
-    {
-      const bf16* l = lraw + t * HK + hl * K;
-      float m = -INFINITY;
-      for (int j = half; j < K; j += 2) m = fmaxf(m, __bfloat162float(l[j]));
-      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-      float sum = 0.f;
-      for (int j = half; j < K; j += 2) sum += __expf(__bfloat162float(l[j]) - m);
-      sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-      const float inv = 1.f / sum;
-      bf16* arow = reinterpret_cast<bf16*>(As + (hl * TT + t) * AS) + t;
-      const unsigned long long i0 = ((static_cast<unsigned long long>(t0 + t) * B + b) * p.H + h0 + hl) * K;
-      for (int j = half; j < K; j += 2) {
-        float w = __expf(__bfloat162float(l[j]) - m) * inv;
-        if (dr.thr) w = drop_val(dr, i0 + j, w);
-        if (on) arow[j] = __float2bfloat16_rn(w);
-      }
-    }
-  }
+  // soft-max of the K taps of every (t, head) into its row of the band matrix, unrolled for the layer's tap count
+  if (K <= 4) band_softmax<2>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
+  else if (K <= 8) band_softmax<4>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
+  else if (K <= 16) band_softmax<8>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
+  else band_softmax<17>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
