@@ -7,6 +7,7 @@
 // memory, and each thread then produces 8 consecutive channels per timestep with 128-bit HBM
 // loads/stores.  HBM traffic = x once (+ a K-1 row halo per extra time tile) + logits once + y once.
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace tnt {
 
@@ -237,6 +238,37 @@ __device__ __forceinline__ void band_softmax(const tnt_dynconv_params& p, const 
   }
 }
 
+// One (gradient row r, head): soft-max statistics (max, 1/sum) of its K taps and its column of the dx band matrix
+// (tap j -> band row s = r - (K-1) + j when 0 <= s < 32); the taps are exponentiated once and kept in registers.
+template <int NJ>
+__device__ __forceinline__ float2 band_column(const bf16* l, int K, int KM, int r, unsigned long long i0, const DropSpec& dr,
+                                              uint8_t* acol, int AS) {
+  float e[NJ];
+  float m = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) {
+    e[j] = j < K ? __bfloat162float(l[j]) : -INFINITY;
+    m = fmaxf(m, e[j]);
+  }
+  float sum = 0.f;
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) {
+    e[j] = j < K ? __expf(e[j] - m) : 0.f;
+    sum += e[j];
+  }
+  const float inv = 1.f / sum;
+  const int j_lo = max(0, KM - r), j_hi = min(K - 1, TT - 1 + KM - r);
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) {
+    if (j >= j_lo && j <= j_hi) {
+      float w = e[j] * inv;
+      if (dr.thr) w = drop_val(dr, i0 + j, w);
+      *reinterpret_cast<bf16*>(acol + j * AS) = __float2bfloat16_rn(w);
+    }
+  }
+  return make_float2(m, inv);
+}
+
 // All global reads of the CTA (window rows, raw tap logits) are issued as cp.async up front: the earlier version's
 // staging loops (load -> store per iteration) serialised one memory latency per iteration and per thread, which --
 // not the arithmetic -- was what kept the kernel at 15 % of the HBM roofline.
@@ -260,13 +292,29 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_tc_kernel(tnt_dynconv_pa
   const int h0 = c0 / R;
 
   const uint32_t xs_s = ptx_smem(xs), lraw_s = ptx_smem(lraw);
-  for (int i = threadIdx.x; i < KW * nv; i += kThreads) {
-    const int r = i / nv, vc = i - r * nv;
-    const int ts = t0 - (K - 1) + r;
-    const uint32_t d = xs_s + r * XS_STRIDE + vc * 16;
-    if (r < rows && ts >= 0) cp_async16(d, x + (static_cast<long>(ts) * B + b) * p.ldx + c0 + vc * 8);
-    else if (r < rows && hist && p.hist_len + ts >= 0) cp_async16(d, hist + (static_cast<long>(p.hist_len + ts) * B + b) * p.C + c0 + vc * 8);
-    else *reinterpret_cast<uint4*>(xs + r * XS_STRIDE + vc * 16) = make_uint4(0, 0, 0, 0);
+  // window rows: ONE bulk copy (512 B, cp.async.bulk -> mbarrier) per row, issued by thread r -- the 16-byte cp.async
+  // form spent 8 loop iterations of 64-bit address arithmetic per thread (a fifth of the kernel's instructions).
+  // Rows [r_h, rows) exist (history before t = 0, then x); the others are zero.
+  uint64_t* bar = reinterpret_cast<uint64_t*>(lraw + TT * HK);
+  const int r_x = max(0, K - 1 - t0);                                    // first row that comes from x
+  const int r_h = hist ? max(0, K - 1 - t0 - p.hist_len) : r_x;          // first row that exists at all
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(bar, 1);
+    ptx::fence_barrier_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) ptx::mbar_arrive_expect_tx(bar, static_cast<uint32_t>(rows - r_h) * CC * 2);
+  if (threadIdx.x >= r_h && threadIdx.x < rows) {
+    const int r = threadIdx.x, ts = t0 - (K - 1) + r;
+    const bf16* src = r >= r_x ? x + (static_cast<long>(ts) * B + b) * p.ldx + c0
+                               : hist + (static_cast<long>(p.hist_len + ts) * B + b) * p.C + c0;
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(xs_s + r * XS_STRIDE), "l"(src), "r"(CC * 2), "r"(ptx_smem(bar)) : "memory");
+  }
+  for (int i = threadIdx.x; i < (r_h + KW - rows) * nv; i += kThreads) {     // the rows that do not exist
+    const int zr = i / nv, vc = i - zr * nv;
+    const int r = zr < r_h ? zr : rows + (zr - r_h);
+    *reinterpret_cast<uint4*>(xs + r * XS_STRIDE + vc * 16) = make_uint4(0, 0, 0, 0);
   }
   {
     const int wpr = HK >> 1;                             // 4-byte words per timestep
@@ -286,13 +334,13 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_tc_kernel(tnt_dynconv_pa
   for (int i = threadIdx.x; i < (HG * TT * AS) / 16; i += kThreads) reinterpret_cast<uint4*>(As)[i] = make_uint4(0, 0, 0, 0);
   cp_async_wait_all();
   __syncthreads();
-  // soft-max of the K taps of every (t, head) and its row of the band matrix: A[hl][t][t + j] = w_j (window row c holds
-  // time t0 - (K-1) + c, so output t reads rows t .. t+K-1); two threads per (t, head) would not pay: 128 x K exps
-  // soft-max of the K taps of every (t, head) into its row of the band matrix, unrolled for the layer's tap count
+  // soft-max of the K taps of every (t, head) into its row of the band matrix: A[hl][t][t + j] = w_j (window row c holds
+  // time t0 - (K-1) + c, so output t reads rows t .. t+K-1), unrolled for the layer's tap count
   if (K <= 4) band_softmax<2>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
   else if (K <= 8) band_softmax<4>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
   else if (K <= 16) band_softmax<8>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
   else band_softmax<17>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
+  ptx::mbar_wait(bar, 0);                                // window rows have landed (async proxy -> visible after the wait)
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -368,13 +416,37 @@ __global__ void __launch_bounds__(kThreads) dynconv_bwd_tc_kernel(tnt_dynconv_bw
   const int h0 = c0 / R;
 
   const uint32_t xw_s = ptx_smem(xw), dw_s = ptx_smem(dw), lraw_s = ptx_smem(lraw);
-  for (int i = threadIdx.x; i < KW * nv; i += kThreads) {
-    const int r = i / nv, vc = i - r * nv;
-    const int ts = t0 - KM + r;
-    if (r < rows_x && ts >= 0) cp_async16(xw_s + r * XS_STRIDE + vc * 16, x + (static_cast<long>(ts) * B + b) * p.ldx + c0 + vc * 8);
-    else *reinterpret_cast<uint4*>(xw + r * XS_STRIDE + vc * 16) = make_uint4(0, 0, 0, 0);
-    if (r < rows_y) cp_async16(dw_s + r * XS_STRIDE + vc * 16, dy + (static_cast<long>(t0 + r) * B + b) * p.lddy + c0 + vc * 8);
-    else *reinterpret_cast<uint4*>(dw + r * XS_STRIDE + vc * 16) = make_uint4(0, 0, 0, 0);
+  // both windows: one 512-byte bulk copy per existing row (threads 0..KW-1: XW rows, threads 128..128+KW-1: DW rows),
+  // completion counted on one mbarrier; rows that do not exist are zero-filled (see the forward kernel)
+  uint64_t* bar = reinterpret_cast<uint64_t*>(stat + KW * HG);
+  const int r_x = max(0, KM - t0);                                       // first XW row that exists
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(bar, 1);
+    ptx::fence_barrier_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) ptx::mbar_arrive_expect_tx(bar, static_cast<uint32_t>(rows_x - r_x + rows_y) * CC * 2);
+  if (threadIdx.x < 128) {
+    const int r = threadIdx.x;
+    if (r >= r_x && r < rows_x)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(xw_s + r * XS_STRIDE), "l"(x + (static_cast<long>(t0 - KM + r) * B + b) * p.ldx + c0), "r"(CC * 2),
+                     "r"(ptx_smem(bar)) : "memory");
+  } else {
+    const int r = threadIdx.x - 128;
+    if (r < rows_y)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(dw_s + r * XS_STRIDE), "l"(dy + (static_cast<long>(t0 + r) * B + b) * p.lddy + c0), "r"(CC * 2),
+                     "r"(ptx_smem(bar)) : "memory");
+  }
+  for (int i = threadIdx.x; i < (r_x + KW - rows_x) * nv; i += kThreads) {
+    const int zr = i / nv, vc = i - zr * nv;
+    const int r = zr < r_x ? zr : rows_x + (zr - r_x);
+    *reinterpret_cast<uint4*>(xw + r * XS_STRIDE + vc * 16) = make_uint4(0, 0, 0, 0);
+  }
+  for (int i = threadIdx.x; i < (KW - rows_y) * nv; i += kThreads) {
+    const int zr = i / nv, vc = i - zr * nv;
+    *reinterpret_cast<uint4*>(dw + (rows_y + zr) * XS_STRIDE + vc * 16) = make_uint4(0, 0, 0, 0);
   }
   {
     const int wpr = HK >> 1;
@@ -390,21 +462,16 @@ __global__ void __launch_bounds__(kThreads) dynconv_bwd_tc_kernel(tnt_dynconv_bw
   for (int i = threadIdx.x; i < rows_y * HG; i += kThreads) {
     const int r = i / HG, hl = i - r * HG;
     const bf16* l = lraw + r * HK + hl * K;
-    float m = -INFINITY;
-    for (int j = 0; j < K; ++j) m = fmaxf(m, __bfloat162float(l[j]));
-    float sum = 0.f;
-    for (int j = 0; j < K; ++j) sum += __expf(__bfloat162float(l[j]) - m);
-    const float inv = 1.f / sum;
-    stat[r * HG + hl] = make_float2(m, inv);
     const unsigned long long i0 = ((static_cast<unsigned long long>(t0 + r) * B + b) * p.H + h0 + hl) * K;
-    const int j_lo = max(0, KM - r), j_hi = min(K - 1, TT - 1 + KM - r);   // input row s = r - (K-1) + j of the tile, 0 <= s < 32
-    for (int j = j_lo; j <= j_hi; ++j) {
-      const int sidx = r - KM + j;
-      float w = __expf(__bfloat162float(l[j]) - m) * inv;
-      if (dr.thr) w = drop_val(dr, i0 + j, w);
-      *reinterpret_cast<bf16*>(As + (hl * TT + sidx) * AS + r * 2) = __float2bfloat16_rn(w);
-    }
+    uint8_t* acol = As + (hl * TT + r - KM) * AS + r * 2;              // tap j lands in band row s = r - (K-1) + j, column r
+    float2 st;                                                           // taps stay in registers between the passes
+    if (K <= 4) st = band_column<4>(l, K, KM, r, i0, dr, acol, AS);
+    else if (K <= 8) st = band_column<8>(l, K, KM, r, i0, dr, acol, AS);
+    else if (K <= 16) st = band_column<16>(l, K, KM, r, i0, dr, acol, AS);
+    else st = band_column<33>(l, K, KM, r, i0, dr, acol, AS);
+    stat[r * HG + hl] = st;
   }
+  ptx::mbar_wait(bar, 0);                                // both windows have landed
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -779,7 +846,7 @@ extern "C" int tnt_dynconv_fwd(const tnt_dynconv_params* p, tnt_stream stream) {
       (reinterpret_cast<uintptr_t>(p->logits) & 3) == 0) {
     const int KW = (tcv::TT + p->K - 1 + 15) & ~15;
     const size_t sm = static_cast<size_t>(KW) * tcv::XS_STRIDE + static_cast<size_t>(tcv::HG) * tcv::TT * (KW * 2 + 16) +
-                      static_cast<size_t>(tcv::TT) * tcv::HG * p->K * 2;
+                      static_cast<size_t>(tcv::TT) * tcv::HG * p->K * 2 + 16;      // + the window's mbarrier
     TNT_TRY(set_smem(tcv::dynconv_fwd_tc_kernel, sm));
     dim3 g2(p->B, p->C / tcv::CC, (p->T + tcv::TT - 1) / tcv::TT);
     TNT_CUDA(launch_pdl(tcv::dynconv_fwd_tc_kernel, g2, dim3(kThreads), sm, as_stream(stream), 1, *p, KW, dr));
@@ -844,7 +911,7 @@ extern "C" int tnt_dynconv_bwd(const tnt_dynconv_bwd_params* p, tnt_stream strea
     const size_t lraw_b = (static_cast<size_t>(KW) * tcv::HG * p->K * 2 + 15) & ~size_t(15);
     const size_t band_b = std::max<size_t>(static_cast<size_t>(tcv::HG) * tcv::TT * (KW * 2 + 16),
                                            static_cast<size_t>(tcv::TT) * tcv::HG * p->K * 4);
-    const size_t sm = 2 * static_cast<size_t>(KW) * tcv::XS_STRIDE + band_b + lraw_b + static_cast<size_t>(KW) * tcv::HG * 8;
+    const size_t sm = 2 * static_cast<size_t>(KW) * tcv::XS_STRIDE + band_b + lraw_b + static_cast<size_t>(KW) * tcv::HG * 8 + 16;   // + the windows' mbarrier
     TNT_TRY(set_smem(tcv::dynconv_bwd_tc_kernel, sm));
     dim3 g2(p->B, p->C / tcv::CC, (p->T + tcv::TT - 1) / tcv::TT);
     tcv::dynconv_bwd_tc_kernel<<<g2, kThreads, sm, as_stream(stream)>>>(*p, KW, dr);
