@@ -283,7 +283,8 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_tc_kernel(tnt_dynconv_pa
   const int HK = HG * K;                                 // tap logits of the CTA's heads per timestep (even)
   uint8_t* xs = smb;                                     // [KW][XS_STRIDE]
   uint8_t* As = xs + KW * XS_STRIDE;                     // [HG][TT][AS]
-  bf16* lraw = reinterpret_cast<bf16*>(As + HG * TT * AS);     // [TT][HK] raw tap logits
+  bf16* lraw = reinterpret_cast<bf16*>(As + HG * TT * AS);     // [TT][LS] raw tap logits
+  const int LS = (((HK * 2 + 15) & ~15) + 16) >> 1;     // row stride (elements): the group's taps + 16-byte alignment slack
   const bf16* x = reinterpret_cast<const bf16*>(p.x);
   const bf16* hist = reinterpret_cast<const bf16*>(p.hist);
   const bf16* lg = reinterpret_cast<const bf16*>(p.logits);
@@ -295,7 +296,13 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_tc_kernel(tnt_dynconv_pa
   // window rows: ONE bulk copy (512 B, cp.async.bulk -> mbarrier) per row, issued by thread r -- the 16-byte cp.async
   // form spent 8 loop iterations of 64-bit address arithmetic per thread (a fifth of the kernel's instructions).
   // Rows [r_h, rows) exist (history before t = 0, then x); the others are zero.
-  uint64_t* bar = reinterpret_cast<uint64_t*>(lraw + TT * HK);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(lraw + TT * LS);
+  // tap logits: the group's H*K-slice of a timestep row starts 8-byte aligned at best, so the bulk copy takes the
+  // enclosing 16-byte-aligned span (it stays inside the row when rows are 16-byte multiples) and the soft-max reads at
+  // the offset `loff`; otherwise 4-byte cp.async
+  const int g0 = h0 * K * 2, a0 = g0 & ~15, lbytes = ((g0 + HK * 2 + 15) & ~15) - a0;
+  const bool lbulk = p.ldl % 8 == 0 && (reinterpret_cast<uintptr_t>(lg) & 15) == 0 && (p.H * K) % 8 == 0;
+  const int loff = lbulk ? (g0 - a0) >> 1 : 0;
   const int r_x = max(0, K - 1 - t0);                                    // first row that comes from x
   const int r_h = hist ? max(0, K - 1 - t0 - p.hist_len) : r_x;          // first row that exists at all
   if (threadIdx.x == 0) {
@@ -303,7 +310,13 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_tc_kernel(tnt_dynconv_pa
     ptx::fence_barrier_init();
   }
   __syncthreads();
-  if (threadIdx.x == 0) ptx::mbar_arrive_expect_tx(bar, static_cast<uint32_t>(rows - r_h) * CC * 2);
+  if (threadIdx.x == 0) ptx::mbar_arrive_expect_tx(bar, static_cast<uint32_t>(rows - r_h) * CC * 2 + (lbulk ? TTl * lbytes : 0));
+  if (lbulk && threadIdx.x >= 64 && threadIdx.x < 64 + TTl) {
+    const int r = threadIdx.x - 64;
+    const uint8_t* src = reinterpret_cast<const uint8_t*>(lg + (static_cast<long>(t0 + r) * B + b) * p.ldl) + a0;
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(lraw_s + r * LS * 2), "l"(src), "r"(lbytes), "r"(ptx_smem(bar)) : "memory");
+  }
   if (threadIdx.x >= r_h && threadIdx.x < rows) {
     const int r = threadIdx.x, ts = t0 - (K - 1) + r;
     const bf16* src = r >= r_x ? x + (static_cast<long>(ts) * B + b) * p.ldx + c0
@@ -316,31 +329,31 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_tc_kernel(tnt_dynconv_pa
     const int r = zr < r_h ? zr : rows + (zr - r_h);
     *reinterpret_cast<uint4*>(xs + r * XS_STRIDE + vc * 16) = make_uint4(0, 0, 0, 0);
   }
-  {
+  if (!lbulk) {
     const int wpr = HK >> 1;                             // 4-byte words per timestep
     const int w0 = threadIdx.x >> 5, l0 = threadIdx.x & 31;          // warp = timestep row, lane = word: no division by K
     if (wpr > 16) {
       for (int r = w0; r < TTl; r += kThreads / 32) {
         const bf16* src = lg + (static_cast<long>(t0 + r) * B + b) * p.ldl + h0 * K;
-        for (int wd = l0; wd < wpr; wd += 32) cp_async4(lraw_s + (r * HK + 2 * wd) * 2, src + 2 * wd);
+        for (int wd = l0; wd < wpr; wd += 32) cp_async4(lraw_s + (r * LS + 2 * wd) * 2, src + 2 * wd);
       }
     } else {                                             // few taps: a row would leave most of a warp idle
       for (int i = threadIdx.x; i < TTl * wpr; i += kThreads) {
         const int r = i / wpr, wd = i - r * wpr;
-        cp_async4(lraw_s + (r * HK + 2 * wd) * 2, lg + (static_cast<long>(t0 + r) * B + b) * p.ldl + h0 * K + 2 * wd);
+        cp_async4(lraw_s + (r * LS + 2 * wd) * 2, lg + (static_cast<long>(t0 + r) * B + b) * p.ldl + h0 * K + 2 * wd);
       }
     }
   }
   for (int i = threadIdx.x; i < (HG * TT * AS) / 16; i += kThreads) reinterpret_cast<uint4*>(As)[i] = make_uint4(0, 0, 0, 0);
   cp_async_wait_all();
+  ptx::mbar_wait(bar, 0);                                // window rows and tap logits have landed (async proxy -> visible)
   __syncthreads();
   // soft-max of the K taps of every (t, head) into its row of the band matrix: A[hl][t][t + j] = w_j (window row c holds
   // time t0 - (K-1) + c, so output t reads rows t .. t+K-1), unrolled for the layer's tap count
-  if (K <= 4) band_softmax<2>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
-  else if (K <= 8) band_softmax<4>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
-  else if (K <= 16) band_softmax<8>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
-  else band_softmax<17>(p, dr, lraw, As, AS, HK, TTl, t0, b, h0);
-  ptx::mbar_wait(bar, 0);                                // window rows have landed (async proxy -> visible after the wait)
+  if (K <= 4) band_softmax<2>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0);
+  else if (K <= 8) band_softmax<4>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0);
+  else if (K <= 16) band_softmax<8>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0);
+  else band_softmax<17>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0);
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -846,7 +859,7 @@ extern "C" int tnt_dynconv_fwd(const tnt_dynconv_params* p, tnt_stream stream) {
       (reinterpret_cast<uintptr_t>(p->logits) & 3) == 0) {
     const int KW = (tcv::TT + p->K - 1 + 15) & ~15;
     const size_t sm = static_cast<size_t>(KW) * tcv::XS_STRIDE + static_cast<size_t>(tcv::HG) * tcv::TT * (KW * 2 + 16) +
-                      static_cast<size_t>(tcv::TT) * tcv::HG * p->K * 2 + 16;      // + the window's mbarrier
+                      static_cast<size_t>(tcv::TT) * (((tcv::HG * p->K * 2 + 15) & ~15) + 16) + 16;   // tap rows + the mbarrier
     TNT_TRY(set_smem(tcv::dynconv_fwd_tc_kernel, sm));
     dim3 g2(p->B, p->C / tcv::CC, (p->T + tcv::TT - 1) / tcv::TT);
     TNT_CUDA(launch_pdl(tcv::dynconv_fwd_tc_kernel, g2, dim3(kThreads), sm, as_stream(stream), 1, *p, KW, dr));
