@@ -196,11 +196,12 @@ __device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-// NJ = taps per thread (two threads per (t, head) row; K <= 2 * NJ - 1 ... 2 * NJ)
-template <int NJ>
+// NJ = taps per thread (two threads per (t, head) row); KT = the tap count when known at compile time (the reference
+// layers' 3 / 7 / 15 / 31: every `j < K` test but the last folds away), 0 = p.K
+template <int NJ, int KT>
 __device__ __forceinline__ void band_softmax(const tnt_dynconv_params& p, const DropSpec& dr, const bf16* lraw, uint8_t* As,
-                                             int AS, int HK, int TTl, int t0, int b, int h0) {
-  const int K = p.K, B = p.B;
+                                             int AS, int LS, int TTl, int t0, int b, int h0) {
+  const int K = KT ? KT : p.K, B = p.B;
   // a warp covers 16 consecutive timesteps of ONE head (head-major: the 4 heads' band rows sit 32 * AS bytes apart,
   // a multiple of 128, so a timestep-major warp stored 4-way bank-conflicted); the thread's <= 17 taps stay in
   // registers between the max, the sum and the store (the three-pass form re-read and re-exponentiated them: the
@@ -209,13 +210,12 @@ __device__ __forceinline__ void band_softmax(const tnt_dynconv_params& p, const 
   const int hl = i / TT, t_raw = i - hl * TT;
   const bool on = t_raw < TTl;                                       // rows beyond the tile: compute on row 0, write nothing
   const int t = on ? t_raw : 0;
-  const bf16* l = lraw + t * HK + hl * K;
+  const bf16* l = lraw + t * LS + hl * K + half;
   float e[NJ];
   float m = -INFINITY;
 #pragma unroll
   for (int jj = 0; jj < NJ; ++jj) {
-    const int j = half + 2 * jj;
-    e[jj] = j < K ? __bfloat162float(l[j]) : -INFINITY;
+    e[jj] = half + 2 * jj < K ? __bfloat162float(l[2 * jj]) : -INFINITY;
     m = fmaxf(m, e[jj]);
   }
   m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
@@ -227,14 +227,17 @@ __device__ __forceinline__ void band_softmax(const tnt_dynconv_params& p, const 
   }
   sum += __shfl_xor_sync(0xffffffffu, sum, 1);
   const float inv = 1.f / sum;
-  bf16* arow = reinterpret_cast<bf16*>(As + (hl * TT + t) * AS) + t;
-  const unsigned long long i0 = ((static_cast<unsigned long long>(t0 + t) * B + b) * p.H + h0 + hl) * K;
+  bf16* arow = reinterpret_cast<bf16*>(As + (hl * TT + t) * AS) + t + half;
+  if (!on) return;
+  if (dr.thr) {
+    const unsigned long long i0 = ((static_cast<unsigned long long>(t0 + t) * B + b) * p.H + h0 + hl) * K + half;
 #pragma unroll
-  for (int jj = 0; jj < NJ; ++jj) {
-    const int j = half + 2 * jj;
-    float w = e[jj] * inv;
-    if (dr.thr && j < K) w = drop_val(dr, i0 + j, w);
-    if (on && j < K) arow[j] = __float2bfloat16_rn(w);
+    for (int jj = 0; jj < NJ; ++jj)
+      if (half + 2 * jj < K) arow[2 * jj] = __float2bfloat16_rn(drop_val(dr, i0 + 2 * jj, e[jj] * inv));
+  } else {
+#pragma unroll
+    for (int jj = 0; jj < NJ; ++jj)
+      if (half + 2 * jj < K) arow[2 * jj] = __float2bfloat16_rn(e[jj] * inv);
   }
 }
 
@@ -350,10 +353,16 @@ __global__ void __launch_bounds__(kThreads) dynconv_fwd_tc_kernel(tnt_dynconv_pa
   __syncthreads();
   // soft-max of the K taps of every (t, head) into its row of the band matrix: A[hl][t][t + j] = w_j (window row c holds
   // time t0 - (K-1) + c, so output t reads rows t .. t+K-1), unrolled for the layer's tap count
-  if (K <= 4) band_softmax<2>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0);
-  else if (K <= 8) band_softmax<4>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0);
-  else if (K <= 16) band_softmax<8>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0);
-  else band_softmax<17>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0);
+  switch (K) {
+    case 3: band_softmax<2, 3>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0); break;
+    case 7: band_softmax<4, 7>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0); break;
+    case 15: band_softmax<8, 15>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0); break;
+    case 31: band_softmax<16, 31>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0); break;
+    default:
+      if (K <= 8) band_softmax<4, 0>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0);
+      else if (K <= 16) band_softmax<8, 0>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0);
+      else band_softmax<17, 0>(p, dr, lraw + loff, As, AS, LS, TTl, t0, b, h0);
+  }
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
