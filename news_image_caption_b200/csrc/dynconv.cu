@@ -241,6 +241,23 @@ __device__ __forceinline__ void band_softmax(const tnt_dynconv_params& p, const 
   }
 }
 
+// soft-max backward of one (t, head) row in place: l[j] <- w_j (g_j - sum_i w_i g_i), w from the stored (max, 1/sum)
+template <int NJ>
+__device__ __forceinline__ void tap_softmax_bwd(bf16* l, const float* g, float2 st, int K) {
+  float w[NJ];
+  float dot = 0.f;
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) {
+    if (j < K) {
+      w[j] = __expf(__bfloat162float(l[j]) - st.x) * st.y;
+      dot = fmaf(w[j], g[j], dot);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NJ; ++j)
+    if (j < K) l[j] = __float2bfloat16_rn(w[j] * (g[j] - dot));
+}
+
 // One (gradient row r, head): soft-max statistics (max, 1/sum) of its K taps and its column of the dx band matrix
 // (tap j -> band row s = r - (K-1) + j when 0 <= s < 32); the taps are exponentiated once and kept in registers.
 template <int NJ>
@@ -594,12 +611,10 @@ __global__ void __launch_bounds__(kThreads) dynconv_bwd_tc_kernel(tnt_dynconv_bw
     bf16* l = lraw + t * HK + hq * K;
     const float2 st = stat[t * HG + hq];
     const float* g = dws + (t * HG + hq) * K;
-    float dot = 0.f;
-    for (int j = 0; j < K; ++j) dot = fmaf(__expf(__bfloat162float(l[j]) - st.x) * st.y, g[j], dot);
-    for (int j = 0; j < K; ++j) {
-      const float w = __expf(__bfloat162float(l[j]) - st.x) * st.y;
-      l[j] = __float2bfloat16_rn(w * (g[j] - dot));
-    }
+    if (K <= 4) tap_softmax_bwd<4>(l, g, st, K);          // taps exponentiated once, kept in registers
+    else if (K <= 8) tap_softmax_bwd<8>(l, g, st, K);
+    else if (K <= 16) tap_softmax_bwd<16>(l, g, st, K);
+    else tap_softmax_bwd<33>(l, g, st, K);
   }
   bf16* dxo = reinterpret_cast<bf16*>(p.dx);
   for (int i = threadIdx.x; i < TTl * nv; i += kThreads) {
