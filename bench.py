@@ -1,15 +1,24 @@
 #!/usr/bin/env python
 """Benchmark of the caption-decoder hot path (BASELINE.json metric: decoder tokens/sec & captions/sec).
 
-Workload (configs[1]): Transform-and-Tell decoder, 4 layers, d=1024, 16 heads, DynamicConv K=3/7/15/31,
-2 sources (49 image feats x 2048, 512 RoBERTa tokens x 1024), caption length 32, batch 64 PER GPU, bf16,
-teacher-forced forward + AdaptiveSoftmax loss over the 50265-BPE vocabulary.  Synthetic inputs, random
-init weights (no dataset / checkpoint offline).  One step = one pass over one batch.
+Headline workload (BASELINE configs[1], C2): Transform-and-Tell decoder, 4 layers, d=1024, 16 heads, DynamicConv
+K=3/7/15/31, 2 sources (49 image feats x 2048, 512 RoBERTa tokens x 1024), caption length 32, batch 64 PER GPU, bf16,
+teacher-forced forward (the API's default path: article attention weights returned) + AdaptiveSoftmax loss over the
+50265-BPE vocabulary.  Synthetic inputs, random-init weights (no dataset / checkpoint offline).  One step = one pass
+over one batch.  The SAME JSON line also carries, under `workloads`, the other BASELINE configs measured in the same
+run -- `train` (C3: fwd+bwd+gradient exchange+BertAdam, the only workload with a collective), `fwd4` (C4: 4-source,
+B=128) and `gen` (C5: greedy generation, B=256, 32 steps) -- each with its own ms_per_step / value / e2e / roofline /
+clocks / parity; plus `parity` (sampled rows of the timed batch against the CPU oracle, outside the timed region),
+`sustained` (a >= 3 s loop of the headline step at whatever clocks the part settles to), `torch_eager_b200` (the
+restated reference on eager ATen/cuBLAS on the same GPU: "the reference PyTorch path" of configs[1]) and
+`cpu_baseline` (+ `cpu_baseline_c1`: configs[0] as stated, B=1).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload all|fwd|train|fwd4|gen]
 """
 import argparse
+import ctypes as C
 import json
+import math
 import os
 import sys
 import threading
@@ -20,20 +29,25 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
-B_PER_GPU, T, S_IMG, S_ART, VOCAB = 64, 32, 49, 512, 50265
-SOURCES = ('image', 'article')
-# --workload: fwd = BASELINE configs[1] (default, the driver-run line); train = configs[2]; fwd4 = configs[3]
-# (NYTimes800k 4-source, B=128); gen = configs[4] (greedy generation, B=256, 32 steps)
+T, S_IMG, S_ART, VOCAB = 32, 49, 512, 50265
+CUT = [5000, 20000, VOCAB]
+SRC2, SRC4 = ('image', 'article'), ('image', 'article', 'faces', 'obj')
+# fwd = BASELINE configs[1] (headline); train = configs[2]; fwd4 = configs[3] (NYTimes800k 4-source); gen = configs[4]
 WORKLOADS = {
-    'fwd': dict(B=64, sources=('image', 'article'), tag='2src', what='fwd+adaptive-loss'),
-    'train': dict(B=64, sources=('image', 'article'), tag='2src', what='TRAIN fwd+bwd+grad-allreduce+BertAdam'),
-    'fwd4': dict(B=128, sources=('image', 'article', 'faces', 'obj'), tag='4src', what='fwd+adaptive-loss'),
-    'gen': dict(B=256, sources=('image', 'article'), tag='2src', what='GREEDY generation 32 steps (incremental DynamicConv ring + cached K/V)'),
+    'fwd': dict(B=64, sources=SRC2, tag='2src', what='fwd(need_attn default)+adaptive-loss'),
+    'train': dict(B=64, sources=SRC2, tag='2src', what='TRAIN fwd+bwd+grad-exchange+BertAdam'),
+    'fwd4': dict(B=128, sources=SRC4, tag='4src', what='fwd(need_attn default)+adaptive-loss'),
+    'gen': dict(B=256, sources=SRC2, tag='2src', what='GREEDY generation 32 steps (incremental DynamicConv ring + cached K/V)'),
 }
-# dram bytes (read + write) of one article K/V GEMM launch from the ncu --set full capture in profiles/ (None until captured)
-TRAFFIC_KV_GEMM = 576.0e6   # profiles/r1_ncu_full_final.txt (final build): 91.1 MB read + 484.9 MB written
+# dram bytes (read + write) per launch from the ncu --set full captures in profiles/ (None until captured)
+TRAFFIC_KV_GEMM = 576.0e6    # profiles/r1_ncu_full_final.txt: 91.1 MB read + 484.9 MB written (article K/V GEMM, B=64)
 TRAFFIC_STEP_ATTN = 389.6e6  # same file, gen workload seed 1234: 385.4 MB read + 4.2 MB written per xattn_step_kernel launch
-WORKLOAD = 'tell-decoder-2src L4 d1024 H16 K3/7/15/31 V50265 fwd+adaptive-loss B64/gpu T32 S49+512'
+
+
+def workload_name(wl):
+    w = WORKLOADS[wl]
+    return 'tell-decoder-%s L4 d1024 H16 K3/7/15/31 V50265 %s B%d/gpu T32 S%s bf16' % (
+        w['tag'], w['what'], w['B'], '49+512' if len(w['sources']) == 2 else '49+512+4+64')
 
 
 def peaks():
@@ -77,33 +91,36 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(n)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.01)
 
     def stop(self):
         self._halt.set()
         self.join(timeout=1)
         s = sorted(self.samples)
-        return {'sm_mhz': s[len(s) // 2] if s else None, 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons)}
+        return {'sm_mhz': s[len(s) // 2] if s else None, 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons),
+                'samples': len(s)}
 
 
-def make_inputs(seed):
+def make_inputs(wl, seed):
     from oracle import synth          # pure torch input generator shared with the tests (no reference code)
-    return synth.make_batch(B_PER_GPU, T, VOCAB, SOURCES, seed=seed, S_img=S_IMG, S_art=S_ART)
+    w = WORKLOADS[wl]
+    return synth.make_batch(w['B'], T, VOCAB, w['sources'], seed=seed, S_img=S_IMG, S_art=S_ART)
 
 
-def cpu_baseline_run(sd, cfg, n_iters, B):
-    """The oracle port (CPU restatement of the reference modules) on this box's host cores: forward +
-    AdaptiveLoss at B captions.  Returns (tokens/s, seconds per iteration list)."""
+# ------------------------------------------------------------------------------------------ CPU legs (oracle port)
+def cpu_forward_loss(sd, sources, B, n_iters, seed=4321):
+    """The oracle port (CPU restatement of the reference modules, pinned against them) on this box's host cores:
+    forward + AdaptiveLoss at B captions.  -> (tokens/s, median seconds per iteration, non-pad tokens)."""
     from oracle import restate as O
     from oracle import synth
-    prev, tgt, ctx = synth.make_batch(B, T, VOCAB, SOURCES, seed=4321, S_img=S_IMG, S_art=S_ART)
+    prev, tgt, ctx = synth.make_batch(B, T, VOCAB, sources, seed=seed, S_img=S_IMG, S_art=S_ART)
     ntok = int((tgt != 1).sum())
     times = []
     with torch.no_grad():
         for i in range(n_iters + 1):
             t0 = time.perf_counter()
-            X, _ = O.decoder_forward(prev, ctx, sd, cfg['heads'], cfg['cutoffs'], cfg['sources'])
-            O.adaptive_nll(X, tgt, sd, cfg['cutoffs'])
+            X, _ = O.decoder_forward(prev, ctx, sd, 16, CUT, list(sources))
+            O.adaptive_nll(X, tgt, sd, CUT)
             dt = time.perf_counter() - t0
             if i > 0:                      # first iteration = warm-up
                 times.append(dt)
@@ -112,25 +129,24 @@ def cpu_baseline_run(sd, cfg, n_iters, B):
 
 
 def run_reference(args, rank):
-    """--impl reference: the reference's CPU implementation of the path (the Python reference cannot travel
-    to the GPU box, so its restatement oracle/restate.py -- pinned against it -- is what runs)."""
+    """--impl reference: the reference's CPU implementation of the path (the Python reference cannot travel to the GPU
+    box, so its restatement oracle/restate.py -- pinned against it -- is what runs), all host threads."""
     if rank != 0:
         return
     from news_image_caption_b200.decoder import random_state_dict
-    cores = len(os.sched_getaffinity(0))
-    torch.set_num_threads(cores)
-    cfg = dict(heads=16, cutoffs=[5000, 20000, VOCAB], sources=['image', 'article'])
-    sd = random_state_dict(seed=0)
-    Bs = 4
     from oracle import restate as O
     from oracle import synth
-    prev, tgt, ctx = synth.make_batch(Bs, T, VOCAB, ('image', 'article'), seed=4321, S_img=S_IMG, S_art=S_ART)
+    cores = len(os.sched_getaffinity(0))
+    torch.set_num_threads(cores)
+    sd = random_state_dict(seed=0)
+    Bs = 4
+    prev, tgt, ctx = synth.make_batch(Bs, T, VOCAB, SRC2, seed=4321, S_img=S_IMG, S_art=S_ART)
     ntok = int((tgt != 1).sum())
 
     def step():
         with torch.no_grad():
-            X, _ = O.decoder_forward(prev, ctx, sd, 16, cfg['cutoffs'], cfg['sources'])
-            return O.adaptive_nll(X, tgt, sd, cfg['cutoffs'])
+            X, _ = O.decoder_forward(prev, ctx, sd, 16, CUT, list(SRC2))
+            return O.adaptive_nll(X, tgt, sd, CUT)
     for _ in range(max(1, min(args.warmup, 2))):
         step()
     t0 = time.perf_counter()
@@ -138,15 +154,455 @@ def run_reference(args, rank):
         step()
     dt = time.perf_counter() - t0
     v = ntok * args.steps / dt
+    c1_v, c1_med, _ = cpu_forward_loss(sd, SRC2, 1, 3)
     print(json.dumps({
         'impl': 'reference', 'metric': 'decoder_tokens_per_sec', 'value': v, 'unit': 'tokens/s', 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * dt / args.steps, 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': WORKLOAD, 'sample': 'B=%d captions per step on the host CPU' % Bs},
+        'config': {'workload': workload_name('fwd'), 'sample': 'B=%d captions per step on the host CPU' % Bs},
         'captions_per_sec': Bs * args.steps / dt,
         'cpu_baseline': {'value': v, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port',
                          'sample': 'oracle port, fp32, B=%d T=32 fwd+loss, %d steps' % (Bs, args.steps)},
+        'cpu_baseline_c1': {'value': c1_v, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port',
+                            'sample': 'BASELINE configs[0] as stated: B=1 T=32 fwd+loss, median of 3 (%.3f s/iter)' % c1_med},
         'e2e': {'value': v, 'unit': 'tokens/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}))
+
+
+# ------------------------------------------------------------------------------------------ helpers of the GPU arm
+class Env:
+    pass
+
+
+def sync_all(env):
+    torch.cuda.synchronize()
+    if env.world > 1:
+        env.dist.barrier()
+        torch.cuda.synchronize()
+
+
+def prof_read(L, name):
+    ms, n = C.c_double(0), C.c_int(0)
+    L.tnt_prof_read(name.encode(), C.byref(ms), C.byref(n))
+    return ms.value, n.value
+
+
+def timed(env, step, steps, warmup, prof_names):
+    """W untimed warm-up steps, then EXACTLY `steps` steps between barrier + synchronize, CUDA events on the launching
+    stream, max over ranks.  -> dict(ms_total, launches, clocks, prof{name: (ms, n)}, out)."""
+    L = env.L
+    out = None
+    for _ in range(warmup):
+        out = step()
+    sync_all(env)
+    sampler = ClockSampler(env.local)
+    sampler.start()
+    L.tnt_prof_reset()
+    L.tnt_prof_enable(1)           # CUDA events around the dominant kernels, on their own stream
+    n0 = L.tnt_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        out = step()
+    e1.record()
+    sync_all(env)
+    launches = L.tnt_launch_count() - n0
+    clocks = sampler.stop()
+    L.tnt_prof_enable(0)
+    prof = {n: prof_read(L, n) for n in prof_names}
+    L.tnt_prof_reset()
+    ms = torch.tensor([e0.elapsed_time(e1)], device='cuda')
+    if env.world > 1:
+        env.dist.all_reduce(ms, op=env.dist.ReduceOp.MAX)
+    return dict(ms_total=ms.item(), launches=int(launches), clocks=clocks, prof=prof, out=out)
+
+
+def all_sum(env, x):
+    t = torch.tensor([float(x)], device='cuda')
+    if env.world > 1:
+        env.dist.all_reduce(t)
+    return t.item()
+
+
+def all_max(env, x):
+    t = torch.tensor([float(x)], device='cuda')
+    if env.world > 1:
+        env.dist.all_reduce(t, op=env.dist.ReduceOp.MAX)
+    return t.item()
+
+
+def peak_for(clocks, tf_burst, tf_sus, which):
+    """The peak that matches the clock the kernel actually ran at: the burst figure when the SM clock sat at (>= 90 % of)
+    its maximum during the timed region, the sustained one when the part had settled lower."""
+    mhz, mx = clocks.get('sm_mhz'), clocks.get('sm_max_mhz')
+    burst = mhz is None or mx is None or mhz >= 0.9 * mx
+    return (tf_burst, which + ' bf16_tflops (burst: SM clock %s of %s MHz during the timed loop)' % (mhz, mx)) if burst else \
+           (tf_sus, which + ' bf16_tflops_sustained (SM clock %s of %s MHz during the timed loop)' % (mhz, mx))
+
+
+def kv_roofline(B, t, ms_per_step):
+    """Dominant kernel of the teacher-forced / training step: the tcgen05 GEMM that projects K/V of the article for all
+    layers, M = S_art * B rows, N = L * 2d, K = 1024; timed by CUDA events inside the timed loop (tnt_prof_*)."""
+    hbm, tf_burst, tf_sus, which = peaks()
+    kv_ms, kv_n = t['prof']['kv_proj.article']
+    M, N, K = S_ART * B, 4 * 2 * 1024, 1024
+    gemm_ms = kv_ms / max(kv_n, 1)
+    flops = 2.0 * M * N * K
+    achieved = flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    peak, src = peak_for(t['clocks'], tf_burst, tf_sus, which)
+    return {'bound': 'tensor', 'kernel': 'gemm_tc_kernel<EPI_NONE,bf16,CG=2> (article K/V projection, all layers)',
+            'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s', 'frac': achieved / peak,
+            'traffic': TRAFFIC_KV_GEMM * B / 64.0 if B == 64 else None, 'peak_source': src,
+            'frac_of_burst_peak': achieved / tf_burst, 'frac_of_sustained_peak': achieved / tf_sus,
+            'flops_per_launch': flops, 'shape': [M, N, K], 'ms_per_launch': gemm_ms, 'launches_timed': kv_n,
+            'share_of_step': gemm_ms / ms_per_step if ms_per_step else None}
+
+
+def sample_rows(ctx, tgt, n):
+    """longest / shortest article, a caption with padding, then a fixed stride -- distinct, sorted."""
+    live = (~ctx['article_mask']).sum(1)
+    rows = {int(live.argmax()), int(live.argmin())}
+    padded = (tgt == 1).any(1).nonzero().view(-1)
+    if len(padded):
+        rows.add(int(padded[0]))
+    B = tgt.shape[0]
+    for r in range(3, B, max(1, B // 7)):
+        if len(rows) >= n:
+            break
+        rows.add(r)
+    return sorted(rows)
+
+
+def sub_batch(ctx, rows):
+    r = torch.as_tensor(rows)
+    return {k: (v[:, r] if v.dim() == 3 else v[r]).contiguous() for k, v in ctx.items()}
+
+
+def parity_forward(dec, sd, sources, prev, tgt, ctx, X, attn, n_rows=4):
+    """Sampled rows of the TIMED batch against the CPU oracle (captions are independent through the decoder): hidden
+    states (relative L2), row-wise full-vocabulary log-probs, loss, attention weights.  Outside every timed region."""
+    from oracle import restate as O
+    rows = sample_rows(ctx, tgt, n_rows)
+    with torch.no_grad():
+        Xo, attn_o = O.decoder_forward(prev[rows], sub_batch(ctx, rows), sd, 16, CUT, list(sources))
+        lpo = O.adaptive_log_prob(Xo, sd, CUT)
+        lo, n_o = O.adaptive_nll(Xo, tgt[rows], sd, CUT)
+    Xs = X[rows]
+    lp = dec.get_normalized_probs((Xs, None)).cpu()
+    ls = dec.nll(Xs, tgt[rows].cuda()).cpu()
+    Xc = Xs.float().cpu()
+    out = {'rows': rows, 'oracle': 'oracle/restate.py fp32 on the host CPU, same rows of the timed batch',
+           'rel_err_X_l2': ((Xc - Xo).norm() / Xo.norm()).item(),
+           'rel_err_logprob_rowwise_max': ((lp - lpo).abs().amax(-1) / lpo.abs().amax(-1)).max().item(),
+           'rel_err_loss': abs(ls[0].item() - lo.item()) / abs(lo.item()), 'n_tokens_equal': int(ls[1].item()) == n_o,
+           'tolerance': 2e-2}
+    if attn is not None:
+        a = attn[rows].cpu()
+        out['rel_err_attn'] = ((a - attn_o).abs().max() / attn_o.abs().max()).item()
+    out['ok'] = bool(out['rel_err_X_l2'] < 2e-2 and out['rel_err_logprob_rowwise_max'] < 2e-2 and out['rel_err_loss'] < 2e-2
+                     and out['n_tokens_equal'] and out.get('rel_err_attn', 0.0) < 2e-2)
+    return out
+
+
+def parity_generation(sd, sources, prev, tgt, ctx, ids, lp, n_rows=3):
+    """The oracle, teacher-forced on the ids the engine generated for the sampled captions, must give those tokens the
+    same log-probs (2e-2) and rank them top-1 up to a bf16 tie."""
+    from oracle import restate as O
+    rows = sample_rows(ctx, tgt, n_rows)
+    ids_c, lp_c = ids.cpu()[rows], lp.cpu()[rows]
+    with torch.no_grad():
+        Xo, _ = O.decoder_forward(ids_c[:, :-1].contiguous(), sub_batch(ctx, rows), sd, 16, CUT, list(sources))
+        lpo = O.adaptive_log_prob(Xo, sd, CUT)
+    done = torch.zeros(len(rows), dtype=torch.bool)
+    worst_lp, worst_gap, n_cmp = 0.0, 0.0, 0
+    for t in range(ids_c.shape[1] - 1):
+        tok = ids_c[:, t + 1]
+        live = ~done
+        if live.any():
+            picked = lpo[live, t].gather(1, tok[live, None])[:, 0]
+            worst_lp = max(worst_lp, ((picked - lp_c[live, t]).abs() / picked.abs().clamp_min(1.0)).max().item())
+            worst_gap = max(worst_gap, (lpo[live, t].max(-1).values - picked).max().item())
+            n_cmp += int(live.sum())
+        done = done | (tok == 2)
+    return {'rows': rows, 'tokens_compared': n_cmp, 'rel_err_picked_logprob_max': worst_lp, 'top1_gap_max_nats': worst_gap,
+            'tolerance': 2e-2, 'oracle': 'oracle/restate.py teacher-forced on the generated ids of the sampled rows',
+            'ok': bool(worst_lp < 2e-2 and worst_gap < 5e-2)}
+
+
+def parity_train(sd, sources, prev, tgt, ctx, dec):
+    """The training step of the timed batch (dropout off for this check) against autograd through the oracle on the WHOLE
+    batch: loss and the worst per-tensor relative-L2 gradient error (the bound tests/test_gpu_train.py uses, 1e-1 in bf16)."""
+    from oracle import restate as O
+    scale = 1.0 / 1024
+    sdl = O.leaf_state_dict(sd, O.tied_output_keys(len(CUT)))
+    Xo, _ = O.decoder_forward(prev, ctx, sdl, 16, CUT, list(sources))
+    lo, n_o = O.adaptive_nll(Xo, tgt, sdl, CUT)
+    (lo * scale).backward()
+    out = dec.train_step(prev.cuda(), tgt.cuda(), {k: v.cuda() for k, v in ctx.items()}, loss_scale=scale).cpu()
+    worst, wk = 0.0, ''
+    for k, p in dec.named_parameters():
+        if 'token_embedder_position' in k:
+            continue
+        g, go = p.grad.float().cpu(), sdl[k].grad
+        e = ((g - go).norm() / go.norm().clamp_min(1e-12)).item()
+        if e > worst:
+            worst, wk = e, k
+    rl = abs(out[0].item() - lo.item()) / abs(lo.item())
+    return {'rows': 'whole batch (%d captions)' % prev.shape[0], 'rel_err_loss': rl, 'n_tokens_equal': int(out[1].item()) == n_o,
+            'grad_rel_l2_worst': worst, 'grad_worst_tensor': wk, 'tolerance': {'loss': 2e-2, 'grad_rel_l2': 1e-1},
+            'oracle': 'autograd through oracle/restate.py (fp32, host CPU), dropout off',
+            'ok': bool(rl < 2e-2 and worst < 1e-1 and int(out[1].item()) == n_o)}
+
+
+# ------------------------------------------------------------------------------------------ the four workloads
+def pin(t):
+    return t.contiguous().pin_memory()
+
+
+def bench_forward(env, wl, dec, sd, args, with_sustained=False):
+    w = WORKLOADS[wl]
+    B = w['B']
+    prev, tgt, ctx = make_inputs(wl, 1234 + env.rank)                     # batch shard of this rank (weak scaling)
+    ntok = int((tgt != 1).sum())
+    prev_d, tgt_d = prev.cuda(), tgt.cuda()
+    ctx_d = {k: (v.cuda().bfloat16() if v.is_floating_point() else v.cuda()) for k, v in ctx.items()}
+    prev_h, tgt_h = pin(prev), pin(tgt)
+    ctx_h = {k: pin(v.bfloat16() if v.is_floating_point() else v) for k, v in ctx.items()}
+    h2d = prev_h.numel() * 8 * 2 + sum(v.numel() * v.element_size() for v in ctx_h.values())
+    keep = {}
+
+    def step():
+        X, ex = dec(prev_d, ctx_d)            # need_attn=True: the mirror's and the reference layer's default (decoder_flattened.py:325)
+        keep['X'], keep['attn'] = X, ex['attn']
+        return dec.nll(X, tgt_d)
+    t = timed(env, step, args.steps, args.warmup, ['kv_proj.article'])
+    loss_check = t['out'].cpu()
+    ntok_all = all_sum(env, ntok)
+    ms_step = t['ms_total'] / args.steps
+    res = {'workload': workload_name(wl), 'ms_per_step': ms_step, 'value': ntok_all * args.steps / (t['ms_total'] * 1e-3),
+           'unit': 'tokens/s', 'captions_per_sec': B * env.world * args.steps / (t['ms_total'] * 1e-3),
+           'gpu_launches': t['launches'], 'clocks': t['clocks'], 'non_pad_tokens_per_step_per_gpu': ntok}
+    # the need_attn=False variant (what round 1 timed) beside it, same loop length
+    t2 = timed(env, lambda: dec.nll(dec(prev_d, ctx_d, need_attn=False)[0], tgt_d), args.steps, 2, [])
+    res['ms_per_step_need_attn_false'] = t2['ms_total'] / args.steps
+
+    # ---- end to end: pinned host buffers -> C ABI (H2D + forward + loss + D2H of the loss), every step; two batches in
+    # flight (submit step i+1, then wait for step i) so the copies of one batch overlap the compute of the other
+    for _ in range(2):
+        dec.score_host(prev_h, tgt_h, ctx_h)
+    sync_all(env)
+    t0 = time.perf_counter()
+    dec.score_host_submit(0, prev_h, tgt_h, ctx_h)
+    for i in range(1, args.steps):
+        dec.score_host_submit(i & 1, prev_h, tgt_h, ctx_h)
+        l_h, n_h = dec.score_host_wait((i - 1) & 1)
+    l_h, n_h = dec.score_host_wait((args.steps - 1) & 1)
+    e2e_s = all_max(env, time.perf_counter() - t0)
+    assert abs(l_h - loss_check[0].item()) < 1e-3 * abs(l_h) and int(n_h) == ntok, (l_h, loss_check, n_h, ntok)
+    res['e2e'] = {'value': ntok_all * args.steps / e2e_s, 'unit': 'tokens/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 8,
+                  'captions_per_sec': B * env.world * args.steps / e2e_s, 'ms_per_step': 1e3 * e2e_s / args.steps}
+    if env.rank == 0:
+        res['roofline'] = kv_roofline(B, t, ms_step)
+        if not args.no_parity:
+            res['parity'] = parity_forward(dec, sd, w['sources'], prev, tgt, ctx, keep['X'], keep['attn'])
+    if with_sustained:
+        # >= 3 s of back-to-back steps: the clocks settle to what the part sustains (MEASURED_PEAKS "sustained" conditions)
+        sync_all(env)
+        sampler = ClockSampler(env.local)
+        sampler.start()
+        n_done, chunk = 0, 200
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t_start = time.perf_counter()
+        while time.perf_counter() - t_start < 3.0:
+            for _ in range(chunk):
+                step()
+            n_done += chunk
+            torch.cuda.synchronize()
+        # the last chunk is the measured one (clocks have settled): events + per-kernel regions
+        env.L.tnt_prof_reset()
+        env.L.tnt_prof_enable(1)
+        e0.record()
+        for _ in range(chunk):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        env.L.tnt_prof_enable(0)
+        clocks = sampler.stop()
+        kv = prof_read(env.L, 'kv_proj.article')
+        env.L.tnt_prof_reset()
+        ms_s = e0.elapsed_time(e1) / chunk
+        hbm, tf_burst, tf_sus, which = peaks()
+        g_ms = kv[0] / max(kv[1], 1)
+        ach = 2.0 * S_ART * B * 8192 * 1024 / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
+        res['sustained'] = {'ms_per_step': ms_s, 'tokens_per_sec_per_gpu': ntok / (ms_s * 1e-3), 'steps_before': n_done,
+                            'steps_timed': chunk, 'seconds': time.perf_counter() - t_start, 'sm_mhz_median': clocks['sm_mhz'],
+                            'sm_max_mhz': clocks['sm_max_mhz'], 'reasons': clocks['reasons'],
+                            'kv_gemm_tflops': ach, 'kv_gemm_frac_of_sustained_peak': ach / tf_sus, 'kv_gemm_ms': g_ms}
+    return res
+
+
+def bench_generation(env, dec, sd, args):
+    w = WORKLOADS['gen']
+    B, GEN = w['B'], T
+    prev, tgt, ctx = make_inputs('gen', 1234 + env.rank)
+    seed_d, seed_h = prev[:, :1].contiguous().cuda(), pin(prev[:, :1])
+    ctx_d = {k: (v.cuda().bfloat16() if v.is_floating_point() else v.cuda()) for k, v in ctx.items()}
+    ctx_h = {k: pin(v.bfloat16() if v.is_floating_point() else v) for k, v in ctx.items()}
+    h2d = seed_h.numel() * 8 + sum(v.numel() * v.element_size() for v in ctx_h.values())
+    steps = max(3, min(args.steps, 10))
+    keep = {}
+
+    def step():
+        keep['lp'], keep['ids'] = dec.generate(seed_d, ctx_d, gen_len=GEN, trim=False)
+        return keep['ids']
+    t = timed(env, step, steps, 2, ['kv_proj.article', 'xattn_step.merged'])
+    ms_step = t['ms_total'] / steps
+    caps = B * env.world * steps / (t['ms_total'] * 1e-3)
+    ids_ref = t['out'].cpu()
+    ids_pin = torch.empty(B, GEN + 1, dtype=torch.long).pin_memory()
+    lp_pin = torch.empty(B, GEN, dtype=torch.float32).pin_memory()
+
+    def e2e_gen():
+        c = {k: v.cuda(non_blocking=True) for k, v in ctx_h.items()}
+        lp, ids = dec.generate(seed_h.cuda(non_blocking=True), c, gen_len=GEN, trim=False)
+        ids_pin.copy_(ids, non_blocking=True)
+        lp_pin.copy_(lp, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    e2e_gen()
+    sync_all(env)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        e2e_gen()
+    e2e_s = all_max(env, time.perf_counter() - t0)
+    assert torch.equal(ids_pin, ids_ref), 'host-buffer generation differs from the device-resident run'
+    res = {'workload': workload_name('gen'), 'metric': 'captions_per_sec', 'ms_per_step': ms_step, 'value': caps, 'unit': 'captions/s',
+           'steps': steps, 'decoder_tokens_per_sec': caps * GEN, 'ms_per_decode_step': ms_step / GEN, 'gpu_launches': t['launches'],
+           'clocks': t['clocks'],
+           'e2e': {'value': B * env.world * steps / e2e_s, 'unit': 'captions/s', 'h2d_bytes_per_step': h2d,
+                   'd2h_bytes_per_step': ids_pin.numel() * 8 + lp_pin.numel() * 4, 'ms_per_step': 1e3 * e2e_s / steps}}
+    if env.rank == 0:
+        hbm, tf_burst, tf_sus, which = peaks()
+        # dominant kernel of a decoding step: cross-attention over the cached K/V of every source of a layer (image + article in
+        # ONE launch, 1 query per head).  Algorithmic bytes = K and V rows of this layer for every LIVE key (padded article
+        # positions are never fetched; + the bias_k/v row and the zero row per source) + q / out
+        live = int((~ctx['article_mask']).sum()) + (S_IMG + 2 + 2) * B
+        byts = live * 2 * 1024 * 2 + 2 * B * 2 * 1024 * 2
+        xs_ms, xs_n = t['prof']['xattn_step.merged']
+        x_ms = xs_ms / max(xs_n, 1)
+        ach = byts / (x_ms * 1e-3) / 1e9 if x_ms > 0 else 0.0
+        res['roofline'] = {'bound': 'hbm', 'kernel': 'xattn_step_kernel: decode-step cross-attention over the cached image + article K/V of one layer (one launch)',
+                           'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': TRAFFIC_STEP_ATTN,
+                           'peak_source': which + ' hbm_gbs', 'bytes_per_launch': byts, 'ms_per_launch': x_ms, 'launches_timed': xs_n,
+                           'live_keys_per_caption': live / B,
+                           'note': 'timed on the eager step 0 of every generate call (steps 1.. replay a CUDA graph)',
+                           'hbm_floor_ms_per_decode_step': (4 * byts + 252e6) / (hbm * 1e9) * 1e3}
+        if not args.no_parity:
+            res['parity'] = parity_generation(sd, w['sources'], prev, tgt, ctx, keep['ids'], keep['lp'])
+        if not args.no_cpu_baseline:
+            from oracle import restate as O
+            from oracle import synth
+            cores = len(os.sched_getaffinity(0))
+            torch.set_num_threads(cores)
+            Bs, Ls = 2, 8
+            p2, _, c2 = synth.make_batch(Bs, T, VOCAB, SRC2, seed=4321, S_img=S_IMG, S_art=S_ART)
+            t0 = time.perf_counter()
+            with torch.no_grad():
+                O.greedy_generate(p2[:, :1], c2, sd, 16, CUT, list(SRC2), gen_len=Ls)
+            dt = time.perf_counter() - t0
+            res['cpu_baseline'] = {'value': Bs / (dt * GEN / Ls), 'unit': 'captions/s', 'cores': cores, 'kind': 'port',
+                                   'sample': 'oracle port greedy loop (reference _generate restated), fp32, B=%d, %d of %d steps timed (%.1f s), scaled linearly to %d steps' % (Bs, Ls, GEN, dt, GEN)}
+    return res
+
+
+def bench_train(env, sd, args):
+    from news_image_caption_b200 import DynamicConvDecoder
+    from news_image_caption_b200.trainer import Trainer
+    w = WORKLOADS['train']
+    B = w['B']
+    dec = DynamicConvDecoder(sources=w['sources'], dtype=torch.bfloat16)
+    dec.load_reference_state_dict(sd)
+    prev, tgt, ctx = make_inputs('train', 1234 + env.rank)
+    ntok = int((tgt != 1).sum())
+    prev_d, tgt_d = prev.cuda(), tgt.cuda()
+    ctx_d = {k: (v.cuda().bfloat16() if v.is_floating_point() else v.cuda()) for k, v in ctx.items()}
+    prev_h, tgt_h = pin(prev), pin(tgt)
+    ctx_h = {k: pin(v.bfloat16() if v.is_floating_point() else v) for k, v in ctx.items()}
+    h2d = prev_h.numel() * 8 * 2 + sum(v.numel() * v.element_size() for v in ctx_h.values())
+    trainer = Trainer(dec, t_total=100000)
+    par = None
+    if env.rank == 0 and env.world == 1 and not args.no_parity:
+        par = parity_train(sd, w['sources'], prev, tgt, ctx, dec)          # before any update, dropout off
+    if not args.no_dropout:     # the reference's training configuration (config.yaml:51-69), counter-based masks, per-rank seeds
+        dec.set_dropout(dropout=0.1, input_dropout=0.1, weight_dropout=0.1, attention_dropout=0.1, relu_dropout=0.0, seed=1234,
+                        rank=env.rank)
+    t = timed(env, lambda: trainer.step(prev_d, tgt_d, ctx_d), args.steps, args.warmup, ['kv_proj.article'])
+    ms_step = t['ms_total'] / args.steps
+    ntok_all = all_sum(env, ntok)
+
+    def e2e_step():
+        c = {k: v.cuda(non_blocking=True) for k, v in ctx_h.items()}
+        o = trainer.step(prev_h.cuda(non_blocking=True), tgt_h.cuda(non_blocking=True), c)
+        return o.cpu()
+    e2e_step()
+    sync_all(env)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        o = e2e_step()
+    e2e_s = all_max(env, time.perf_counter() - t0)
+    res = {'workload': workload_name('train') + (' (dropout p=0)' if args.no_dropout else ' (dropout 0.1 / input 0.1 / weight 0.1 / attention 0.1 as config.yaml)'),
+           'ms_per_step': ms_step, 'value': ntok_all * args.steps / (t['ms_total'] * 1e-3), 'unit': 'tokens/s',
+           'captions_per_sec': B * env.world * args.steps / (t['ms_total'] * 1e-3), 'gpu_launches': t['launches'], 'clocks': t['clocks'],
+           'collective': trainer.exchange_description() if env.world > 1 else 'none at N=1',
+           'loss_bits_per_token_last': float(o[0]) / max(float(o[1]), 1.0) / math.log(2.0),
+           'e2e': {'value': ntok_all * args.steps / e2e_s, 'unit': 'tokens/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 8,
+                   'ms_per_step': 1e3 * e2e_s / args.steps}}
+    if env.rank == 0:
+        res['roofline'] = kv_roofline(B, t, ms_step)
+        if par is not None:
+            res['parity'] = par
+    del trainer, dec
+    torch.cuda.empty_cache()
+    return res
+
+
+def torch_eager_b200(sd, args):
+    """The restated reference (oracle/restate.py: the reference modules' arithmetic as plain eager ATen / cuBLAS calls) on
+    THIS GPU, forward + AdaptiveLoss at the headline batch: "the reference PyTorch path" of BASELINE configs[1].  A
+    comparator printed beside the number -- never on the product path."""
+    from oracle import restate as O
+    prev, tgt, ctx = make_inputs('fwd', 1234)
+    ntok = int((tgt != 1).sum())
+    out = {'what': 'oracle/restate.py forward + adaptive loss on CUDA tensors (eager ATen/cuBLAS, no CUDA graph, CUDA_LAUNCH_BLOCKING unset), B=64 T=32',
+           'unit': 'tokens/s'}
+    try:
+        sdc = {k: v.cuda() for k, v in sd.items()}
+        pd, td = prev.cuda(), tgt.cuda()
+        cd = {k: v.cuda() for k, v in ctx.items()}
+        for name, ac in (('fp32', None), ('bf16_autocast', torch.bfloat16)):
+            def step():
+                with torch.no_grad():
+                    if ac is None:
+                        X, _ = O.decoder_forward(pd, cd, sdc, 16, CUT, list(SRC2))
+                        return O.adaptive_nll(X, td, sdc, CUT)[0]
+                    with torch.autocast('cuda', dtype=ac):
+                        X, _ = O.decoder_forward(pd, cd, sdc, 16, CUT, list(SRC2))
+                        return O.adaptive_nll(X, td, sdc, CUT)[0]
+            for _ in range(3):
+                loss = step()
+            torch.cuda.synchronize()
+            n = 10
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(n):
+                loss = step()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / n
+            out[name] = {'ms_per_step': ms, 'value': ntok / (ms * 1e-3), 'loss_sum': float(loss)}
+        del sdc
+        torch.cuda.empty_cache()
+    except Exception as e:      # the comparator must never take the benchmark down
+        out['error'] = '%s: %s' % (type(e).__name__, str(e)[:200])
+    return out
 
 
 def main():
@@ -156,17 +612,12 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
-    ap.add_argument('--workload', default='fwd', choices=sorted(WORKLOADS),
-                    help='fwd = BASELINE configs[1] (the default, driver-run line); train = configs[2]; fwd4 = configs[3]; gen = configs[4]')
+    ap.add_argument('--no-parity', action='store_true', help='skip the sampled-row oracle checks (outside the timed regions anyway)')
+    ap.add_argument('--no-eager', action='store_true', help='skip the torch-eager-on-this-GPU comparator')
+    ap.add_argument('--workload', default='all', choices=['all'] + sorted(WORKLOADS),
+                    help='all = headline fwd line + workloads{train,fwd4,gen} (the driver-run default); or one workload alone')
     ap.add_argument('--no-dropout', action='store_true', help='train workload: the p = 0 parity configuration instead of config.yaml dropout')
     args = ap.parse_args()
-    global B_PER_GPU, SOURCES, WORKLOAD
-    wl = dict(WORKLOADS[args.workload])
-    if args.workload == 'train':
-        wl['what'] += ' (dropout p=0)' if args.no_dropout else ' (dropout 0.1 / input 0.1 / weight 0.1 / attention 0.1 as config.yaml)'
-    B_PER_GPU, SOURCES = wl['B'], wl['sources']
-    WORKLOAD = 'tell-decoder-%s L4 d1024 H16 K3/7/15/31 V50265 %s B%d/gpu T32 S%s' % (
-        wl['tag'], wl['what'], B_PER_GPU, '49+512' if len(SOURCES) == 2 else '49+512+4+64')
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
     local = int(os.environ.get('LOCAL_RANK', 0))
@@ -176,7 +627,6 @@ def main():
 
     import torch.distributed as dist
     from news_image_caption_b200 import DynamicConvDecoder, _lib, build
-    from news_image_caption_b200 import ops
     from news_image_caption_b200.decoder import random_state_dict
     torch.cuda.set_device(local)
     if world > 1:
@@ -186,203 +636,76 @@ def main():
     if world > 1:
         dist.barrier()
     _lib.require_device()
-    L = _lib.lib()
+    env = Env()
+    env.rank, env.world, env.local, env.dist, env.L = rank, world, local, dist, _lib.lib()
+    which = ['fwd', 'train', 'fwd4', 'gen'] if args.workload == 'all' else [args.workload]
 
-    sd = random_state_dict(seed=0, sources=SOURCES)
-    dec = DynamicConvDecoder(sources=SOURCES, dtype=torch.bfloat16)
-    dec.load_reference_state_dict(sd)
-    dec.prepare()
-    prev, tgt, ctx = make_inputs(1234 + rank)                     # batch shard of this rank (weak scaling)
-    ntok = int((tgt != 1).sum())
-    prev_d, tgt_d = prev.cuda(), tgt.cuda()
-    ctx_d = {k: (v.cuda().bfloat16() if v.is_floating_point() else v.cuda()) for k, v in ctx.items()}
-    # host-side (pinned) copies for the end-to-end arm
-    pin = lambda t: t.contiguous().pin_memory()
-    prev_h, tgt_h = pin(prev), pin(tgt)
-    ctx_h = {k: pin(v.bfloat16() if v.is_floating_point() else v) for k, v in ctx.items()}
-    h2d = prev_h.numel() * 8 * 2 + sum(v.numel() * v.element_size() for v in ctx_h.values())
-
-    trainer = None
-    if args.workload == 'train':
-        from news_image_caption_b200.trainer import Trainer
-        trainer = Trainer(dec, t_total=100000)
-        if not args.no_dropout:     # the reference's training configuration (config.yaml:51-69), counter-based masks
-            dec.set_dropout(dropout=0.1, input_dropout=0.1, weight_dropout=0.1, attention_dropout=0.1, relu_dropout=0.0, seed=1234)
-
-    gen = args.workload == 'gen'
-    GEN_LEN = T
-    if gen:
-        ntok = B_PER_GPU * GEN_LEN                   # tokens produced per step (finished rows keep their slot)
-        seed_d, seed_h = prev_d[:, :1].contiguous(), pin(prev[:, :1])
-        h2d = seed_h.numel() * 8 + sum(v.numel() * v.element_size() for v in ctx_h.values())
-
-    def step():
-        if trainer is not None:
-            return trainer.step(prev_d, tgt_d, ctx_d)
-        if gen:
-            lp, ids = dec.generate(seed_d, ctx_d, gen_len=GEN_LEN, trim=False)
-            return ids
-        X, _ = dec(prev_d, ctx_d, need_attn=False)
-        return dec.nll(X, tgt_d)
-
-    def sync_all():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    for _ in range(args.warmup):
-        out = step()
-    loss_check = out.cpu()
-    sync_all()
-    sampler = ClockSampler(local)
-    sampler.start()
-    L.tnt_prof_reset()
-    L.tnt_prof_enable(1)           # CUDA events around the K/V projection GEMM, on its own stream
-    n0 = L.tnt_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        step()
-    e1.record()
-    sync_all()
-    launches = L.tnt_launch_count() - n0
-    clocks = sampler.stop()
-    L.tnt_prof_enable(0)
-    import ctypes as C
-    kv_ms, kv_n = C.c_double(0), C.c_int(0)
-    L.tnt_prof_read(b'kv_proj.article', C.byref(kv_ms), C.byref(kv_n))
-    xs_ms, xs_n = C.c_double(0), C.c_int(0)
-    L.tnt_prof_read(b'xattn_step.merged', C.byref(xs_ms), C.byref(xs_n))
-    L.tnt_prof_reset()
-    ms = torch.tensor([e0.elapsed_time(e1)], device='cuda')
-    ntok_all = torch.tensor([float(ntok)], device='cuda')
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        dist.all_reduce(ntok_all)
-    ms_total = ms.item()
-    value = ntok_all.item() * args.steps / (ms_total * 1e-3)
-
-    # ---- end to end: pinned host buffers -> C ABI (H2D + forward + loss + D2H of the loss), every step.
-    # Two batches are in flight (submit step i+1, then wait for step i): the H2D copies of one batch overlap
-    # the compute of the other; every step still copies all of its inputs from pinned host memory.
-    d2h = 8
-    if gen:
-        ids_ref = out.cpu()
-        ids_pin = torch.empty(B_PER_GPU, GEN_LEN + 1, dtype=torch.long).pin_memory()
-        lp_pin = torch.empty(B_PER_GPU, GEN_LEN, dtype=torch.float32).pin_memory()
-        d2h = ids_pin.numel() * 8 + lp_pin.numel() * 4
-
-        def e2e_gen():
-            c = {k: v.cuda(non_blocking=True) for k, v in ctx_h.items()}
-            lp, ids = dec.generate(seed_h.cuda(non_blocking=True), c, gen_len=GEN_LEN, trim=False)
-            ids_pin.copy_(ids, non_blocking=True)
-            lp_pin.copy_(lp, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-        for _ in range(2):
-            e2e_gen()
-        sync_all()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            e2e_gen()
-        assert torch.equal(ids_pin, ids_ref), 'host-buffer generation differs from the device-resident run'
-    elif trainer is not None:
-        def e2e_step():
-            c = {k: v.cuda(non_blocking=True) for k, v in ctx_h.items()}
-            o = trainer.step(prev_h.cuda(non_blocking=True), tgt_h.cuda(non_blocking=True), c)
-            return o.cpu()
-        for _ in range(2):
-            e2e_step()
-        sync_all()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            o = e2e_step()
-        l_h, n_h = float(o[0]), float(o[1]) / world
-        loss_check = torch.tensor([l_h])         # parameters move every step: nothing to compare against
-    else:
-        for _ in range(2):
-            dec.score_host(prev_h, tgt_h, ctx_h)
-        sync_all()
-        t0 = time.perf_counter()
-        dec.score_host_submit(0, prev_h, tgt_h, ctx_h)
-        for i in range(1, args.steps):
-            dec.score_host_submit(i & 1, prev_h, tgt_h, ctx_h)
-            l_h, n_h = dec.score_host_wait((i - 1) & 1)
-        l_h, n_h = dec.score_host_wait((args.steps - 1) & 1)
-    e2e_s = torch.tensor([time.perf_counter() - t0], device='cuda')
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_value = ntok_all.item() * args.steps / e2e_s.item()
-    assert trainer is not None or gen or (abs(l_h - loss_check[0].item()) < 1e-3 * abs(l_h) and int(n_h) == ntok), (l_h, loss_check, n_h, ntok)
+    sd2 = random_state_dict(seed=0, sources=SRC2)
+    results = {}
+    dec2 = None
+    if 'fwd' in which or 'gen' in which:
+        dec2 = DynamicConvDecoder(sources=SRC2, dtype=torch.bfloat16)
+        dec2.load_reference_state_dict(sd2)
+        dec2.prepare()
+    if 'fwd' in which:
+        results['fwd'] = bench_forward(env, 'fwd', dec2, sd2, args, with_sustained=True)
+    if 'gen' in which:
+        results['gen'] = bench_generation(env, dec2, sd2, args)
+    dec2 = None
+    torch.cuda.empty_cache()
+    if 'fwd4' in which:
+        sd4 = random_state_dict(seed=0, sources=SRC4)
+        dec4 = DynamicConvDecoder(sources=SRC4, dtype=torch.bfloat16)
+        dec4.load_reference_state_dict(sd4)
+        dec4.prepare()
+        results['fwd4'] = bench_forward(env, 'fwd4', dec4, sd4, args)
+        del dec4, sd4
+        torch.cuda.empty_cache()
+    if 'train' in which:
+        results['train'] = bench_train(env, sd2, args)
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel: the tcgen05 GEMM that projects K/V of the article for all layers
-    hbm, tf_burst, tf_sus, which = peaks()
-    # measured live: CUDA events around this launch inside the timed loop above (tnt_prof_*), averaged
-    M, N, K = S_ART * B_PER_GPU, 4 * 2 * 1024, 1024
-    gemm_ms = kv_ms.value / max(kv_n.value, 1)
-    flops = 2.0 * M * N * K
-    achieved = flops / (gemm_ms * 1e-3) / 1e12
-    roofline = {'bound': 'tensor', 'kernel': 'gemm_tc_kernel<EPI_NONE,bf16> (article K/V projection, all layers)',
-                'achieved': achieved, 'peak': tf_sus, 'unit': 'TFLOP/s', 'frac': achieved / tf_sus,
-                'traffic': TRAFFIC_KV_GEMM, 'peak_source': which + ' bf16_tflops_sustained (kernel timed inside the step loop)',
-                'frac_of_burst_peak': achieved / tf_burst,
-                'shape': [M, N, K], 'ms_per_launch': gemm_ms, 'launches_timed': kv_n.value,
-                'share_of_step': gemm_ms / (ms_total / args.steps)}
-
-    if gen:
-        # dominant kernel of a decoding step: cross-attention over the cached K/V of every source of a layer (image +
-        # article in ONE launch, 1 query per head).  Algorithmic bytes = K and V rows of this layer for every LIVE key
-        # (padded article positions are never fetched; + the bias_k/v row and the zero row per source) + q / out
-        live = int((~ctx['article_mask']).sum()) + (S_IMG + 2 + 2) * B_PER_GPU
-        byts = live * 2 * 1024 * 2 + 2 * B_PER_GPU * 2 * 1024 * 2
-        x_ms = xs_ms.value / max(xs_n.value, 1)
-        ach = byts / (x_ms * 1e-3) / 1e9 if x_ms > 0 else 0.0
-        roofline = {'bound': 'hbm', 'kernel': 'xattn_step_kernel: decode-step cross-attention over the cached image + article K/V of one layer (one launch)',
-                    'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': TRAFFIC_STEP_ATTN,
-                    'peak_source': which + ' hbm_gbs', 'bytes_per_launch': byts, 'ms_per_launch': x_ms,
-                    'launches_timed': xs_n.value, 'live_keys_per_caption': live / B_PER_GPU, 'note': 'timed on the eager step 0 of every generate call (steps 1.. replay a CUDA graph)',
-                    'kv_proj_gemm_tflops': achieved, 'kv_proj_ms': gemm_ms}
-    cpu = None
-    if not args.no_cpu_baseline and gen:
+    head_name = 'fwd' if 'fwd' in results else which[0]
+    head = results.pop(head_name)
+    gen_head = head_name == 'gen'
+    line = {
+        'metric': 'captions_per_sec' if gen_head else 'decoder_tokens_per_sec', 'value': head['value'], 'unit': head['unit'],
+        'n_gpus': world, 'steps': head.get('steps', args.steps), 'warmup': args.warmup, 'ms_per_step': head['ms_per_step'],
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+        'config': {'workload': head['workload'],
+                   'l2': 'per-step working set (K/V 0.5 GB + activations) exceeds the 126 MB L2',
+                   'non_pad_tokens_per_step_per_gpu': head.get('non_pad_tokens_per_step_per_gpu')},
+        'captions_per_sec': head.get('captions_per_sec', head['value']),
+        'decoder_tokens_per_sec': head.get('decoder_tokens_per_sec', head['value']),
+        'e2e': head['e2e'], 'gpu_launches': head['gpu_launches'], 'clocks': head['clocks'], 'roofline': head.get('roofline'),
+    }
+    for k in ('ms_per_step_need_attn_false', 'parity', 'sustained', 'ms_per_decode_step'):
+        if k in head:
+            line[k] = head[k]
+    cpu = head.get('cpu_baseline')
+    if cpu is None and not args.no_cpu_baseline and not gen_head:
         cores = len(os.sched_getaffinity(0))
         torch.set_num_threads(cores)
-        from oracle import restate as O
-        from oracle import synth
-        Bs, Ls = 2, 8
-        p2, _, c2 = synth.make_batch(Bs, T, VOCAB, SOURCES, seed=4321, S_img=S_IMG, S_art=S_ART)
-        t0 = time.perf_counter()
-        with torch.no_grad():
-            O.greedy_generate(p2[:, :1], c2, sd, 16, [5000, 20000, VOCAB], list(SOURCES), gen_len=Ls)
-        dt = time.perf_counter() - t0
-        cpu = {'value': Bs / (dt * GEN_LEN / Ls), 'unit': 'captions/s', 'cores': cores, 'kind': 'port',
-               'sample': 'oracle port greedy loop (reference _generate restated), fp32, B=%d, %d of %d steps timed (%.1f s), scaled linearly to %d steps' % (Bs, Ls, GEN_LEN, dt, GEN_LEN)}
-    elif not args.no_cpu_baseline:
-        cores = len(os.sched_getaffinity(0))
-        torch.set_num_threads(cores)
-        cfg = dict(heads=16, cutoffs=[5000, 20000, VOCAB], sources=['image', 'article'])
-        cfg['sources'] = list(SOURCES)
-        v, med, nt = cpu_baseline_run(sd, cfg, 3, 4)
+        v, med, nt = cpu_forward_loss(sd2, SRC2, 4, 3)
         cpu = {'value': v, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port',
                'sample': 'oracle port (restated reference modules), fp32, B=4 T=32 fwd+loss, median of 3 (%.2f s/iter)' % med}
-
-    caps = B_PER_GPU * world * args.steps / (ms_total * 1e-3)
-    caps_e2e = B_PER_GPU * world * args.steps / e2e_s.item()
-    print(json.dumps({
-        'metric': 'captions_per_sec' if gen else 'decoder_tokens_per_sec', 'value': caps if gen else value,
-        'unit': 'captions/s' if gen else 'tokens/s', 'n_gpus': world, 'steps': args.steps,
-        'warmup': args.warmup, 'ms_per_step': ms_total / args.steps, 'higher_is_better': True, 'scaling': 'weak',
-        'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
-        'config': {'workload': WORKLOAD, 'l2': 'per-step working set (K/V 0.5 GB + activations) exceeds the 126 MB L2',
-                   'non_pad_tokens_per_step_per_gpu': ntok},
-        'captions_per_sec': caps, 'decoder_tokens_per_sec': value,
-        'e2e': {'value': caps_e2e if gen else e2e_value, 'unit': 'captions/s' if gen else 'tokens/s',
-                'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h, 'captions_per_sec': caps_e2e},
-        'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roofline, 'cpu_baseline': cpu}))
+        if world == 1:
+            v1, med1, _ = cpu_forward_loss(sd2, SRC2, 1, 3)
+            line['cpu_baseline_c1'] = {'value': v1, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port',
+                                       'sample': 'BASELINE configs[0] as stated: B=1 T=32 fwd+loss, fp32, median of 3 (%.3f s/iter)' % med1}
+    line['cpu_baseline'] = cpu
+    if world == 1 and not args.no_eager and 'fwd' == head_name:
+        line['torch_eager_b200'] = torch_eager_b200(sd2, args)
+        for k in ('fp32', 'bf16_autocast'):
+            if k in line['torch_eager_b200']:
+                line['torch_eager_b200'][k]['speedup_ours'] = line['value'] / line['torch_eager_b200'][k]['value']
+    if results:
+        line['workloads'] = results
+    print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 

@@ -218,7 +218,14 @@ typedef struct {
   const int* start_pos;          /* DEVICE incremental offset or NULL (0) */
   int B, T, d, n_pos, pad_idx;
   int dtype;
+  /* id / position guard (nn.Embedding raises IndexError for an id outside [0, vocab), adaptive.py:61-76; the reference
+   * grows the sinusoid table on demand, positional.py:231-268).  vocab > 0: a row whose id is out of range is written as
+   * NaN and bit TNT_DEVERR_TOKEN_ID is OR-ed into *error_flags; a position beyond the table reads its last row and sets
+   * TNT_DEVERR_POSITION.  vocab == 0 / error_flags == NULL: unchecked ids (the caller guarantees the range). */
+  int vocab;
+  int* error_flags;              /* DEVICE int or NULL */
 } tnt_embed_params;
+enum { TNT_DEVERR_TOKEN_ID = 1, TNT_DEVERR_POSITION = 2 };
 int tnt_embed_fwd(const tnt_embed_params* p, tnt_stream stream);
 
 /* ------------------------------------------------------------------------------------------
@@ -352,6 +359,8 @@ typedef struct {
   int pad_idx;                             /* 1: positions + loss ignore_index */
   int max_positions;                       /* rows of the sinusoid table */
   int dtype;                               /* TNT_BF16 or TNT_F32 (parity mode) */
+  int embed_padding_idx;                   /* nn.Embedding(padding_idx) of every adaptive band table: that band-LOCAL row gets
+                                              no gradient (adaptive.py:42; config.yaml:39 says 0).  < 0 = none */
 } tnt_decoder_config;
 
 typedef struct tnt_decoder tnt_decoder;
@@ -405,6 +414,9 @@ int tnt_decoder_generate_beam(tnt_decoder* d, const int64_t* seed, const tnt_con
 /* embedder output (adaptive band embedding * sqrt(d) + sinusoidal position, decoder_flattened.py:96-99) for ids [B, T]:
  * out [T*B, d] engine dtype, row t*B + b (the layout the layers run on).  The pointer decoder's `inp_embed`. */
 int tnt_decoder_embed(tnt_decoder* d, const int64_t* ids, int B, int T, void* out_tb, tnt_stream stream);
+/* Device-side input errors seen by this decoder's kernels since the last call (TNT_DEVERR_* bits, cleared on read):
+ * a token id outside [0, vocab) or a position beyond the sinusoid table.  Synchronises `stream`. */
+int tnt_decoder_error_flags(tnt_decoder* d, tnt_stream stream);
 
 /* Copy head of DynamicConvDecoderPointer (decoder_pointer.py:138-141, 151-216), in place on the
  * full-vocabulary log-probabilities of tnt_decoder_log_prob:
@@ -487,6 +499,18 @@ int tnt_decoder_train_step(tnt_decoder* d, const int64_t* ids, const int64_t* ta
 int tnt_decoder_train_stages(const tnt_decoder* d);
 int tnt_decoder_stream_wait_stage(tnt_decoder* d, int stage, tnt_stream stream);
 
+/* Data-parallel training, sparse embedding gradient.  The band tables are tied to the softmax output rows: their gradient
+ * is a dense softmax part (final at stage 0, so its exchange overlaps the whole backward) plus <= B*T embedding rows that
+ * only exist when the backward ends.  With buffers registered here the step does NOT scatter those rows into the dense
+ * tables; it packs them -- rows [B*T, d] engine dtype, meta[j] = band << 32 | band-local row, *count = rows written -- so
+ * the ranks can all-gather B*T rows (4 MB in bf16) instead of all-reducing the 206 MB tables a second time, and each rank
+ * applies every rank's list with tnt_embed_grad_scatter.  rows == NULL switches back to the dense scatter.
+ * In this mode the band tables ("...embeddings.i.0.weight") are final at stage 0; the band projections at the last stage. */
+int tnt_decoder_set_sparse_embed_grad(tnt_decoder* d, void* rows, int64_t* meta, int* count, int capacity_rows);
+int tnt_embed_grad_scatter(const void* rows, int64_t ld_rows, const int64_t* meta, const int* count, int max_rows,
+                           float* const* band_grads, const int* band_dims, int n_bands, int skip_row, int dtype,
+                           tnt_stream stream);
+
 /* Fused BertAdam step over flat fp32 arenas (the reference's optimizer: config.yaml:126-136, `bert_adam`):
  * g' = grad_scale * (*grad_scale_dev) * g, clipped PER PARAMETER TENSOR to max_grad_norm (segments),
  * m = b1 m + (1-b1) g', v = b2 v + (1-b2) g'^2, p -= lr * (m / (sqrt(v) + eps) + weight_decay * p).
@@ -522,6 +546,12 @@ int tnt_decoder_score_host_wait(tnt_decoder* d, int slot);
 
 /* number of kernels this library has launched since load (for bench.py's gpu_launches) */
 uint64_t tnt_launch_count(void);
+/* Which kernel VARIANT the dispatchers picked since load: launches counted under `name` (-1 = unknown name; NULL resets
+ * every counter).  Names: gemm.tc.1cta, gemm.tc.pair (cta_group::2), gemm.splitk, gemm.simt, xattn.tc,
+ * xattn.tc.tileskip (all-padding key tiles skipped), xattn.tc.weights (head-averaged weights from the tcgen05 kernel),
+ * xattn.simt, xattn.step, xattn_bwd.tc, xattn_bwd.simt, dynconv.{fwd,bwd}.{tc,simt}, dynconv.step.{fast,simt}.
+ * Tests use it to pin that the code the benchmark times is the code the parity tests ran. */
+int64_t tnt_variant_count(const char* name);
 
 /* Named device-time regions, timed with CUDA events on the launching stream (off by default).
  * Regions: "kv_proj.<source>" (the K/V projection GEMM of tnt_decoder_forward / _generate / _train).

@@ -87,7 +87,8 @@ class LayernormBwdParams(C.Structure):
 
 class EmbedParams(C.Structure):
     _fields_ = [('ids', vp), ('table', vp), ('pos_table', vp), ('out', vp), ('ldo', i64), ('start_pos', vp),
-                ('B', i32), ('T', i32), ('d', i32), ('n_pos', i32), ('pad_idx', i32), ('dtype', i32)]
+                ('B', i32), ('T', i32), ('d', i32), ('n_pos', i32), ('pad_idx', i32), ('dtype', i32), ('vocab', i32),
+                ('error_flags', vp)]
 
 
 class ContextMixParams(C.Structure):
@@ -130,7 +131,7 @@ class DecoderConfig(C.Structure):
     _fields_ = [('n_layers', i32), ('d', i32), ('heads', i32), ('ffn', i32), ('vocab', i32),
                 ('kernels', i32 * MAX_LAYERS), ('n_sources', i32), ('source_names', (C.c_char * 16) * MAX_SOURCES),
                 ('source_dim', i32 * MAX_SOURCES), ('n_clusters', i32), ('cutoffs', i32 * MAX_CLUSTERS),
-                ('pad_idx', i32), ('max_positions', i32), ('dtype', i32)]
+                ('pad_idx', i32), ('max_positions', i32), ('dtype', i32), ('embed_padding_idx', i32)]
 
 
 class Contexts(C.Structure):
@@ -143,6 +144,7 @@ _SIGS = {
     'tnt_last_error': (C.c_char_p, []),
     'tnt_device_check': (i32, []),
     'tnt_launch_count': (C.c_uint64, []),
+    'tnt_variant_count': (C.c_int64, [C.c_char_p]),
     'tnt_prof_enable': (None, [i32]),
     'tnt_prof_reset': (None, []),
     'tnt_prof_read': (i32, [C.c_char_p, C.POINTER(C.c_double), C.POINTER(i32)]),
@@ -176,6 +178,7 @@ _SIGS = {
     'tnt_decoder_nll': (i32, [vp, vp, vp, i32, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_log_prob': (i32, [vp, vp, i32, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_embed': (i32, [vp, vp, i32, i32, vp, vp]),
+    'tnt_decoder_error_flags': (i32, [vp, vp]),
     'tnt_pointer_mix': (i32, [C.POINTER(PointerParams), vp]),
     'tnt_nll_rows': (i32, [vp, i64, vp, i32, i32, vp, vp]),
     'tnt_decoder_generate_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
@@ -194,6 +197,8 @@ _SIGS = {
     'tnt_decoder_set_dropout': (i32, [vp, C.POINTER(DropoutConfig)]),
     'tnt_decoder_train_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
     'tnt_decoder_set_grad': (i32, [vp, C.c_char_p, vp]),
+    'tnt_decoder_set_sparse_embed_grad': (i32, [vp, vp, vp, vp, i32]),
+    'tnt_embed_grad_scatter': (i32, [vp, i64, vp, vp, i32, C.POINTER(vp), C.POINTER(i32), i32, i32, i32, vp]),
     'tnt_decoder_train_step': (i32, [vp, vp, vp, C.POINTER(Contexts), f32, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_train_stages': (i32, [vp]),
     'tnt_decoder_stream_wait_stage': (i32, [vp, i32, vp]),

@@ -259,7 +259,13 @@ static bool g_force_simt_attn = false;
 bool xattn_force_simt() { return g_force_simt_attn; }
 int xattn_fwd_dispatch(const tnt_xattn_params* p, cudaStream_t st) {
   if (!g_force_simt_attn && xattn_step_supported(p)) return xattn_fwd_step(p, st);      // T == 1: HBM-streaming decode kernel
-  if (!g_force_simt_attn && xattn_tc_supported(p)) return xattn_fwd_tc(p, st);
+  if (!g_force_simt_attn && xattn_tc_supported(p)) {
+    variant_hit(V_XATTN_TC);
+    if (p->tile_live) variant_hit(V_XATTN_TC_TILESKIP);
+    if (p->weights) variant_hit(V_XATTN_TC_WEIGHTS);
+    return xattn_fwd_tc(p, st);
+  }
+  variant_hit(V_XATTN_SIMT);
   return xattn_fwd_simt(p, st);
 }
 

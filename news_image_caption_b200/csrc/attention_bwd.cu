@@ -253,7 +253,11 @@ int xattn_bwd(const XattnBwd* p, cudaStream_t st) {
   TNT_CHECK_ARG(p->f.n_extra == 0, "xattn_bwd: materialise the bias_k / zero rows in k, v (n_extra must be 0)");
   TNT_CHECK_ARG(p->scratch != nullptr, "xattn_bwd: fp32 scratch [B,H,T,D] missing");
   if (p->f.T == 0 || p->f.B == 0) return TNT_OK;
-  if (!g_force_simt_attn_bwd && xattn_bwd_tc_supported(p)) return xattn_bwd_tc(p, st);
+  if (!g_force_simt_attn_bwd && xattn_bwd_tc_supported(p)) {
+    variant_hit(V_XATTN_BWD_TC);
+    return xattn_bwd_tc(p, st);
+  }
+  variant_hit(V_XATTN_BWD_SIMT);
   BwdArgs a;
   a.f = p->f;
   a.scratch = p->scratch;

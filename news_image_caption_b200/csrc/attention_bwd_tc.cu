@@ -475,11 +475,10 @@ int xattn_bwd_tc(const XattnBwd* p, cudaStream_t st) {
   a.n_qt = (f.T + abt::TQ - 1) / abt::TQ;
   a.n_items = f.B * (f.H / 2);
   a.n_tiles = (f.S + abt::TKEYS - 1) / abt::TKEYS;
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.first()) {
     TNT_CUDA(cudaFuncSetAttribute(abt::xattn_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, abt::SMEM_BYTES));
     TNT_CUDA(cudaFuncSetAttribute(abt::xattn_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, abt::SMEM_BYTES));
-    attr = true;
   }
   const int grid = std::min(a.n_items, num_sms());
   if (a.drop.thr) abt::xattn_bwd_tc_kernel<true><<<grid, abt::kThreads, abt::SMEM_BYTES, st>>>(tmQ, tmDO, tmK, tmV, a);

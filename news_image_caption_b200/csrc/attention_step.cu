@@ -283,6 +283,7 @@ int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int
   // are co-resident anyway -- so the static mapping stays the default; TNT_STEP_ATTN_DYNAMIC=1 switches the queue on
   static const bool dyn = [] { const char* e = getenv("TNT_STEP_ATTN_DYNAMIC"); return e && e[0] == '1'; }();
   batch.sched = dyn ? sched : nullptr;
+  variant_hit(V_XATTN_STEP);
   const int total = n * ps[0].B * (ps[0].H / kHeadsPerCta);
   static const int per_sm = [] { const char* e = getenv("TNT_STEP_ATTN_CTAS_PER_SM"); return e ? std::max(1, atoi(e)) : 4; }();
   dim3 grid(batch.sched ? std::min(total, per_sm * num_sms()) : total);

@@ -44,6 +44,8 @@ struct Args {
   int n_items, n_qt, n_tiles;
   DropSpec drop;                                  // dropout on the probabilities (the normaliser stays un-dropped)
   const uint32_t* tile_live;                      // optional [B]: bit i set = key tile i of batch row b holds an un-masked key
+  float* weights;                                 // optional [B, T, S] fp32, ZEROED by the launcher: head-averaged probabilities
+  float inv_heads;                                //   (multi_head.py:478-482), accumulated with red.global.add by a third pass
 };
 
 // Work list in shared memory: entry = batch row | (key tiles to visit) << 16.  Tiles whose keys are all padding contribute
@@ -331,7 +333,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&bar->s_empty);        // score columns may be overwritten
+      if (!a.weights && lane == 0) ptx::mbar_arrive(&bar->s_empty);        // score columns may be overwritten
       // column sums across the warp, then across the 4 quadrant warps of this head
       float mysum = 0.f;
 #pragma unroll
@@ -341,6 +343,39 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       red_sum[lane] = mysum;
       named_bar(3, 256);                 // the epilogue reads the sums of BOTH head groups
+      if (a.weights) {
+        // ---- pass 3 (last decoder layer only): head-averaged attention weights.  The scores are still resident in TMEM
+        // and the normalisers are final, so every probability is rebuilt exactly as pass 2 made it, scaled by
+        // 1 / (l * H) and added to weights[b, t, key]: the 8 head pairs of a caption land on the same row through
+        // red.global.add (lanes = consecutive keys: one 128-byte reduction per warp and query).  Masked keys add nothing.
+        const float* rsl = red + 256 + hd * 128;
+        const float lsum = rsl[lane] + rsl[32 + lane] + rsl[64 + lane] + rsl[96 + lane];
+        const float my_inv = lsum > 0.f ? a.inv_heads / lsum : 0.f;          // column (query) `lane`
+        uint32_t ml = live;
+        for (int i = 0; i < nl; ++i, ml &= ml - 1) {
+          const int tile = __ffs(ml) - 1;
+          uint32_t v[32];
+          ptx::tmem_ld_32x32(tmem + lane_base + i * 64 + hd * 32, v);
+          ptx::tmem_ld_wait();
+          const bool ok = (valid >> i) & 1;
+          const int key = tile * TKEYS + quad * 32 + lane;
+          float* wrow = a.weights + (static_cast<long>(b) * a.T + qt * TQ) * a.S + key;
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            const float inv = __shfl_sync(0xffffffffu, my_inv, c);
+            float pw = exp2f(fmaf(__uint_as_float(v[c]), a.scale_log2e, -mx[c]));
+            if (DROP) {
+              const unsigned long long i0 =
+                  ((static_cast<unsigned long long>(b) * a.H + hp * 2 + hd) * a.T + qt * TQ + c) * a.S + tile * TKEYS + quad * 32 + lane;
+              pw = drop_val(a.drop, i0, pw);
+            }
+            if (ok && qt * TQ + c < a.T) atomicAdd(wrow + static_cast<long>(c) * a.S, pw * inv);
+          }
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&bar->s_empty);
+      }
       if (a.lse && quad == 0) {          // log-sum-exp of the scaled scores, saved for the backward pass
         const float* rsl = red + 256 + hd * 128;
         const float l = rsl[lane] + rsl[32 + lane] + rsl[64 + lane] + rsl[96 + lane];
@@ -392,7 +427,7 @@ int xattn_tile_mask(const uint8_t* mask, long m_stride_b, int B, int S, int mask
 }
 
 bool xattn_tc_supported(const tnt_xattn_params* p) {
-  if (p->dtype != TNT_BF16 || p->D != 64 || (p->H & 1) || p->n_extra != 0 || p->weights || p->kv_group > 1) return false;
+  if (p->dtype != TNT_BF16 || p->D != 64 || (p->H & 1) || p->n_extra != 0 || p->kv_group > 1) return false;
   if (p->mask_mode != TNT_MASK_NONE && p->mask_mode != TNT_MASK_KEY_PADDING) return false;
   if (p->S < 1 || p->S > atc::MAX_TILES * atc::TKEYS) return false;
   const long strides = p->q_stride_t | p->q_stride_b | p->k_stride_s | p->k_stride_b | p->v_stride_s | p->v_stride_b;
@@ -415,14 +450,17 @@ int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st) {
   a.lse = p->lse; a.scale = p->scale;
   a.drop = make_drop(p->drop);
   a.tile_live = p->tile_live;
+  a.weights = p->weights;
+  a.inv_heads = 1.f / static_cast<float>(p->H);
+  // the kernel accumulates the weights with reductions (and never visits all-padding tiles): start from zero
+  if (p->weights) TNT_CUDA(cudaMemsetAsync(p->weights, 0, sizeof(float) * static_cast<size_t>(p->B) * p->T * p->S, st));
   a.n_qt = (p->T + atc::TQ - 1) / atc::TQ;
   a.n_items = p->B * (p->H / 2) * a.n_qt;
   a.n_tiles = (p->S + atc::TKEYS - 1) / atc::TKEYS;
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.first()) {
     TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
     TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
-    attr = true;
   }
   const int grid = std::min(a.n_items, num_sms());
   if (a.drop.thr)

@@ -226,15 +226,71 @@ __global__ void __launch_bounds__(256) gather_table_kernel(const float* table, l
 
 template <typename T>
 __global__ void __launch_bounds__(256) scatter_table_kernel(const T* src, long lds, const int* loc, const int* count,
-                                                            float* grad, long ldg, int C) {
+                                                            float* grad, long ldg, int C, int skip_row) {
   const int lane = threadIdx.x & 31;
   const int n = *count;
   for (int j = blockIdx.x * 8 + (threadIdx.x >> 5); j < n; j += gridDim.x * 8) {
     const int l = loc[j];
-    if (l == 0) continue;                                 // nn.Embedding(padding_idx=0): no gradient
+    if (l == skip_row) continue;                          // nn.Embedding(padding_idx): that row gets no gradient
     const T* s = src + static_cast<long>(j) * lds;
     float* d = grad + static_cast<long>(l) * ldg;
     for (int vc = lane; vc < (C >> 3); vc += 32) {
+      float v[8];
+      load8(s + vc * 8, v);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) atomicAdd(d + vc * 8 + i, v[i]);
+    }
+  }
+}
+
+// Sparse form of the embedding-table gradient (data-parallel training): instead of scattering the rows into the dense band
+// table, band `band`'s rows are appended to a packed list -- row j lands at offset sum_{k < band} count[k] + j with
+// meta = band << 32 | band-local row -- that the ranks all-gather and every rank scatters (embed_grad_scatter).
+template <typename T>
+__global__ void __launch_bounds__(256) pack_band_rows_kernel(const T* src, long lds, const int* loc, const int* counts, int band,
+                                                             T* rows_out, long ldo, long long* meta, int* total, int C, int n_bands) {
+  const int lane = threadIdx.x & 31;
+  int off = 0;
+  for (int k = 0; k < band; ++k) off += counts[k];
+  const int n = counts[band];
+  if (blockIdx.x == 0 && threadIdx.x == 0 && band == n_bands - 1) *total = off + n;
+  for (int j = blockIdx.x * 8 + (threadIdx.x >> 5); j < n; j += gridDim.x * 8) {
+    const T* s = src + static_cast<long>(j) * lds;
+    T* o = rows_out + static_cast<long>(off + j) * ldo;
+    for (int vc = lane; vc < (C >> 3); vc += 32) *reinterpret_cast<uint4*>(o + vc * 8) = *reinterpret_cast<const uint4*>(s + vc * 8);
+    if (lane == 0) meta[off + j] = (static_cast<long long>(band) << 32) | static_cast<unsigned>(loc[j]);
+  }
+}
+template <>
+__global__ void __launch_bounds__(256) pack_band_rows_kernel<float>(const float* src, long lds, const int* loc, const int* counts,
+                                                                    int band, float* rows_out, long ldo, long long* meta,
+                                                                    int* total, int C, int n_bands) {
+  const int lane = threadIdx.x & 31;
+  int off = 0;
+  for (int k = 0; k < band; ++k) off += counts[k];
+  const int n = counts[band];
+  if (blockIdx.x == 0 && threadIdx.x == 0 && band == n_bands - 1) *total = off + n;
+  for (int j = blockIdx.x * 8 + (threadIdx.x >> 5); j < n; j += gridDim.x * 8) {
+    const float* s = src + static_cast<long>(j) * lds;
+    float* o = rows_out + static_cast<long>(off + j) * ldo;
+    for (int vc = lane; vc < (C >> 2); vc += 32) *reinterpret_cast<float4*>(o + vc * 4) = *reinterpret_cast<const float4*>(s + vc * 4);
+    if (lane == 0) meta[off + j] = (static_cast<long long>(band) << 32) | static_cast<unsigned>(loc[j]);
+  }
+}
+
+struct BandTables { float* grad[TNT_MAX_CLUSTERS]; int dim[TNT_MAX_CLUSTERS]; };
+template <typename T>
+__global__ void __launch_bounds__(256) embed_grad_scatter_kernel(const T* rows, long ldr, const long long* meta, const int* count,
+                                                                 int max_rows, BandTables bt, int n_bands, int skip_row) {
+  const int lane = threadIdx.x & 31;
+  const int n = min(*count, max_rows);
+  for (int j = blockIdx.x * 8 + (threadIdx.x >> 5); j < n; j += gridDim.x * 8) {
+    const long long m = meta[j];
+    const int band = static_cast<int>(m >> 32), l = static_cast<int>(m & 0xffffffffll);
+    if (band < 0 || band >= n_bands || l == skip_row) continue;
+    const T* s = rows + static_cast<long>(j) * ldr;
+    float* d = bt.grad[band] + static_cast<long>(l) * bt.dim[band];
+    for (int vc = lane; vc < (bt.dim[band] >> 3); vc += 32) {
       float v[8];
       load8(s + vc * 8, v);
 #pragma unroll
@@ -427,13 +483,27 @@ int gather_table_rows(const float* table, long ldt, const int* loc, const int* c
 }
 
 int scatter_table_grad(const void* src, long lds, const int* loc, const int* count, int max_rows, float* grad, long ldg,
-                       int C, int dtype, cudaStream_t st) {
+                       int C, int dtype, int skip_row, cudaStream_t st) {
   if (max_rows == 0) return TNT_OK;
   const int grid = grid_for(max_rows, 8);
   if (dtype == TNT_BF16)
-    scatter_table_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<const bf16*>(src), lds, loc, count, grad, ldg, C);
+    scatter_table_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<const bf16*>(src), lds, loc, count, grad, ldg, C, skip_row);
   else
-    scatter_table_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(src), lds, loc, count, grad, ldg, C);
+    scatter_table_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(src), lds, loc, count, grad, ldg, C, skip_row);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+int pack_band_rows(const void* src, long lds, const int* loc, const int* counts, int band, int n_bands, int max_rows, void* rows_out,
+                   long ldo, long long* meta, int* total, int C, int dtype, cudaStream_t st) {
+  if (max_rows == 0) return TNT_OK;
+  const int grid = grid_for(max_rows, 8);
+  if (dtype == TNT_BF16)
+    pack_band_rows_kernel<bf16><<<grid, 256, 0, st>>>(static_cast<const bf16*>(src), lds, loc, counts, band, static_cast<bf16*>(rows_out),
+                                                      ldo, meta, total, C, n_bands);
+  else
+    pack_band_rows_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(src), lds, loc, counts, band,
+                                                       static_cast<float*>(rows_out), ldo, meta, total, C, n_bands);
   TNT_LAUNCHED();
   return TNT_OK;
 }
@@ -477,3 +547,31 @@ int add_col_blocks(void* dst, long ldd, const void* src, long lds, int N, int C,
 }
 
 }  // namespace tnt
+
+// Applies one rank's packed embedding-gradient rows (tnt_decoder_set_sparse_embed_grad) to the dense fp32 band-table
+// gradients: grad[band][loc] += row for every listed row; the band-local padding row is skipped (adaptive.py:42).
+extern "C" int tnt_embed_grad_scatter(const void* rows, int64_t ld_rows, const int64_t* meta, const int* count, int max_rows,
+                                      float* const* band_grads, const int* band_dims, int n_bands, int skip_row, int dtype,
+                                      tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(rows && meta && count && band_grads && band_dims && n_bands >= 1 && n_bands <= TNT_MAX_CLUSTERS,
+                "embed_grad_scatter: bad arguments");
+  if (max_rows <= 0) return TNT_OK;
+  BandTables bt = {};
+  for (int i = 0; i < n_bands; ++i) {
+    TNT_CHECK_ARG(band_grads[i] && band_dims[i] % 8 == 0, "embed_grad_scatter: band %d", i);
+    bt.grad[i] = band_grads[i];
+    bt.dim[i] = band_dims[i];
+  }
+  const int grid = grid_for(max_rows, 8);
+  if (dtype == TNT_BF16)
+    embed_grad_scatter_kernel<bf16><<<grid, 256, 0, as_stream(stream)>>>(static_cast<const bf16*>(rows), ld_rows,
+                                                                         reinterpret_cast<const long long*>(meta), count, max_rows, bt,
+                                                                         n_bands, skip_row);
+  else
+    embed_grad_scatter_kernel<float><<<grid, 256, 0, as_stream(stream)>>>(static_cast<const float*>(rows), ld_rows,
+                                                                          reinterpret_cast<const long long*>(meta), count, max_rows, bt,
+                                                                          n_bands, skip_row);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}

@@ -36,9 +36,13 @@ int gather_rows(const void* src, long lds, const int* rows, const int* count, in
 // out[j, :] = table[loc[j], :] (fp32 table -> engine dtype) for j < *count
 int gather_table_rows(const float* table, long ldt, const int* loc, const int* count, int max_rows, void* out, long ldo,
                       int C, int dtype, cudaStream_t st);
-// grad[loc[j], :] += src[j, :] (fp32 atomics; local row 0 = the band's padding_idx is skipped, adaptive.py:42,51)
+// grad[loc[j], :] += src[j, :] (fp32 atomics; local row `skip_row` = the band's padding_idx is skipped, adaptive.py:42,51)
 int scatter_table_grad(const void* src, long lds, const int* loc, const int* count, int max_rows, float* grad, long ldg,
-                       int C, int dtype, cudaStream_t st);
+                       int C, int dtype, int skip_row, cudaStream_t st);
+
+// sparse embedding gradient: append band `band`'s rows (src[j], j < counts[band]) to the packed list (see backward.cu)
+int pack_band_rows(const void* src, long lds, const int* loc, const int* counts, int band, int n_bands, int max_rows, void* rows_out,
+                   long ldo, long long* meta, int* total, int C, int dtype, cudaStream_t st);
 
 // dst[r, 0:C] += sum_{s0 <= s < ns} src[r, s*C : (s+1)*C]   (the residual fan-in of the per-source branches)
 int add_col_blocks(void* dst, long ldd, const void* src, long lds, int N, int C, int s0, int ns, int dtype,

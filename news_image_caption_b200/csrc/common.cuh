@@ -12,6 +12,16 @@ namespace tnt {
 // ------------------------------------------------------------------ host side: errors, launches
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
+// which kernel VARIANT a dispatcher picked (tnt_variant_count): lets a test pin that the code path a benchmark times is
+// the one the parity tests exercised (CTA-pair GEMM, split-K plan, tile-skipping attention, ...)
+enum Variant {
+  V_GEMM_TC_1CTA, V_GEMM_TC_PAIR, V_GEMM_SPLITK, V_GEMM_SIMT,
+  V_XATTN_TC, V_XATTN_TC_TILESKIP, V_XATTN_TC_WEIGHTS, V_XATTN_SIMT, V_XATTN_STEP,
+  V_XATTN_BWD_TC, V_XATTN_BWD_SIMT,
+  V_DYNCONV_FWD_TC, V_DYNCONV_FWD_SIMT, V_DYNCONV_BWD_TC, V_DYNCONV_BWD_SIMT, V_DYNCONV_STEP_FAST, V_DYNCONV_STEP_SIMT,
+  V_LN_GEMM_FUSED, V_COUNT
+};
+void variant_hit(Variant v);
 bool prof_enabled();
 int prof_begin(const char* name, cudaStream_t st);   // -1 when profiling is off
 void prof_end(int id, cudaStream_t st);
@@ -88,15 +98,30 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 inline size_t dtype_size(int dt) { return dt == TNT_BF16 ? 2 : 4; }
-inline int num_sms() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
+// per-DEVICE caches: one process may drive several GPUs (cudaFuncSetAttribute and the SM count are per device)
+constexpr int kMaxDevices = 64;
+inline int cur_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev & (kMaxDevices - 1);
+}
+struct PerDeviceOnce {          // `static PerDeviceOnce once; if (once.first()) { ...set attributes... }`
+  bool done[kMaxDevices] = {};
+  bool first() {
+    const int d = cur_device();
+    if (done[d]) return false;
+    done[d] = true;
+    return true;
   }
-  return n;
+};
+inline int num_sms() {
+  static int n[kMaxDevices] = {};
+  const int dev = cur_device();
+  if (!n[dev]) {
+    cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (n[dev] <= 0) n[dev] = 148;
+  }
+  return n[dev];
 }
 inline cudaStream_t as_stream(tnt_stream s) { return reinterpret_cast<cudaStream_t>(s); }
 

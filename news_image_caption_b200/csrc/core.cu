@@ -1,6 +1,7 @@
 // Library-wide plumbing: error string, launch counter, device check.
 #include <stdarg.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include <atomic>
 #include <mutex>
@@ -28,6 +29,14 @@ bool pdl_enabled() {
   }
   return g_pdl != 0;
 }
+static std::atomic<uint64_t> g_variants[V_COUNT];
+static const char* const kVariantNames[V_COUNT] = {
+    "gemm.tc.1cta", "gemm.tc.pair", "gemm.splitk", "gemm.simt",
+    "xattn.tc", "xattn.tc.tileskip", "xattn.tc.weights", "xattn.simt", "xattn.step",
+    "xattn_bwd.tc", "xattn_bwd.simt",
+    "dynconv.fwd.tc", "dynconv.fwd.simt", "dynconv.bwd.tc", "dynconv.bwd.simt", "dynconv.step.fast", "dynconv.step.simt",
+    "gemm.ln_fused"};
+void variant_hit(Variant v) { g_variants[v].fetch_add(1, std::memory_order_relaxed); }
 void count_launch(int n) { g_launches.fetch_add(static_cast<uint64_t>(n), std::memory_order_relaxed); }
 
 // ---- named device-time regions (CUDA events on the launching stream), off by default.
@@ -61,6 +70,17 @@ void prof_end(int id, cudaStream_t st) {
 extern "C" int tnt_version(void) { return 100; }
 extern "C" const char* tnt_last_error(void) { return tnt::g_err; }
 extern "C" uint64_t tnt_launch_count(void) { return tnt::g_launches.load(); }
+
+// launches of dispatcher variant `name` since load (-1: unknown name); name == NULL resets every counter
+extern "C" int64_t tnt_variant_count(const char* name) {
+  if (!name) {
+    for (auto& v : tnt::g_variants) v.store(0);
+    return 0;
+  }
+  for (int i = 0; i < tnt::V_COUNT; ++i)
+    if (!strcmp(name, tnt::kVariantNames[i])) return static_cast<int64_t>(tnt::g_variants[i].load());
+  return -1;
+}
 
 extern "C" int tnt_device_check(void) {
   int dev = 0, major = 0;

@@ -888,6 +888,7 @@ extern "C" int tnt_dynconv_fwd(const tnt_dynconv_params* p, tnt_stream stream) {
     dim3 g2(p->B, p->C / tcv::CC, (p->T + tcv::TT - 1) / tcv::TT);
     TNT_CUDA(launch_pdl(tcv::dynconv_fwd_tc_kernel, g2, dim3(kThreads), sm, as_stream(stream), 1, *p, KW, dr));
     TNT_LAUNCHED();
+    variant_hit(V_DYNCONV_FWD_TC);
     return TNT_OK;
   }
   if (p->dtype == TNT_BF16) {
@@ -898,6 +899,7 @@ extern "C" int tnt_dynconv_fwd(const tnt_dynconv_params* p, tnt_stream stream) {
     TNT_CUDA(launch_pdl(dynconv_fwd_kernel<float>, grid, dim3(kThreads), smem, as_stream(stream), 1, *p, CC, HG, dr));
   }
   TNT_LAUNCHED();
+  variant_hit(V_DYNCONV_FWD_SIMT);
   return TNT_OK;
 }
 
@@ -915,6 +917,7 @@ extern "C" int tnt_dynconv_step(const tnt_dynconv_step_params* p, tnt_stream str
     TNT_TRY(set_smem(dynconv_step_fast_kernel, sm2));
     TNT_CUDA(launch_pdl(dynconv_step_fast_kernel, dim3(p->B), dim3(nv * kStepGroups), sm2, as_stream(stream), 1, *p));
     TNT_LAUNCHED();
+    variant_hit(V_DYNCONV_STEP_FAST);
     return TNT_OK;
   }
   if (p->dtype == TNT_BF16)
@@ -922,6 +925,7 @@ extern "C" int tnt_dynconv_step(const tnt_dynconv_step_params* p, tnt_stream str
   else
     TNT_CUDA(launch_pdl(dynconv_step_kernel<float>, dim3(p->B), dim3(kThreads), smem, as_stream(stream), 1, *p));
   TNT_LAUNCHED();
+  variant_hit(V_DYNCONV_STEP_SIMT);
   return TNT_OK;
 }
 
@@ -953,6 +957,7 @@ extern "C" int tnt_dynconv_bwd(const tnt_dynconv_bwd_params* p, tnt_stream strea
     dim3 g2(p->B, p->C / tcv::CC, (p->T + tcv::TT - 1) / tcv::TT);
     tcv::dynconv_bwd_tc_kernel<<<g2, kThreads, sm, as_stream(stream)>>>(*p, KW, dr);
     TNT_LAUNCHED();
+    variant_hit(V_DYNCONV_BWD_TC);
     return TNT_OK;
   }
   if (p->dtype == TNT_BF16) {
@@ -963,5 +968,6 @@ extern "C" int tnt_dynconv_bwd(const tnt_dynconv_bwd_params* p, tnt_stream strea
     dynconv_bwd_kernel<float><<<grid, kThreads, smem, as_stream(stream)>>>(*p, CC, HG, dr);
   }
   TNT_LAUNCHED();
+  variant_hit(V_DYNCONV_BWD_SIMT);
   return TNT_OK;
 }

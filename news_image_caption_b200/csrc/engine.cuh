@@ -50,6 +50,7 @@ struct tnt_decoder {
   float* kvrow[TNT_MAX_SOURCES] = {};  // [L*2d] the learned bias_k | bias_v row of every layer (extra key S)
   void* table = nullptr;               // [vocab, d] pre-projected, pre-scaled embedding
   float* pos_table = nullptr;          // [max_positions, d]
+  int* err_flags = nullptr;            // device int: TNT_DEVERR_* bits raised by the embedding kernels
   tnt::AdaSoftmax ada;
   void* scratch_dd = nullptr;          // [d, d] fp32 (finalize only)
   void* emb_scratch = nullptr;             // largest band table in the engine dtype (finalize only)
@@ -59,6 +60,8 @@ struct tnt_decoder {
   int emb_dim[TNT_MAX_CLUSTERS] = {};
   std::vector<cudaEvent_t> stage_events;   // training: gradients of stage i are final (tnt_decoder_stream_wait_stage)
   std::map<std::string, float*> grads; // training: fp32 gradient buffer per state_dict key (tnt_decoder_set_grad)
+  // data-parallel training: embedding-row gradients go to a packed list instead of the dense band tables
+  void* sparse_rows = nullptr; long long* sparse_meta = nullptr; int* sparse_count = nullptr; int sparse_capacity = 0;
   int article_idx = -1;   // source whose head-averaged attention the forward returns ("entity" if present, else "article")
   tnt_dropout_config drop_cfg = {};    // training dropout (tnt_decoder_set_dropout); all zero = off
   uint64_t drop_step = 0;              // training steps issued since the configuration was set

@@ -241,6 +241,7 @@ int embed(tnt_decoder* D, const int64_t* ids, int B, int T, void* out, const int
   tnt_embed_params e = {};
   e.ids = ids; e.table = D->table; e.pos_table = D->pos_table; e.out = out; e.ldo = D->cfg.d; e.start_pos = start_pos;
   e.B = B; e.T = T; e.d = D->cfg.d; e.n_pos = D->cfg.max_positions; e.pad_idx = D->cfg.pad_idx; e.dtype = D->cfg.dtype;
+  e.vocab = D->cfg.vocab; e.error_flags = D->err_flags;
   return tnt_embed_fwd(&e, st);
 }
 
@@ -287,6 +288,16 @@ extern "C" int tnt_decoder_embed(tnt_decoder* D, const int64_t* ids, int B, int 
   TNT_CHECK_ARG(D && D->finalized && ids && out_tb && B > 0 && T > 0, "decoder_embed: bad arguments");
   TNT_CHECK_ARG(T + D->cfg.pad_idx + 1 <= D->cfg.max_positions, "decoder_embed: T=%d exceeds the position table", T);
   return embed(D, ids, B, T, out_tb, nullptr, as_stream(stream));
+}
+
+extern "C" int tnt_decoder_error_flags(tnt_decoder* D, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->err_flags, "decoder_error_flags: decoder has no weight memory bound");
+  int flags = 0;
+  cudaStream_t st = as_stream(stream);
+  TNT_CUDA(cudaMemcpyAsync(&flags, D->err_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+  TNT_CUDA(cudaStreamSynchronize(st));
+  if (flags) TNT_CUDA(cudaMemsetAsync(D->err_flags, 0, sizeof(int), st));
+  return flags;
 }
 
 extern "C" int tnt_decoder_nll(tnt_decoder* D, const void* X, const int64_t* target, int n_rows, float* out2,

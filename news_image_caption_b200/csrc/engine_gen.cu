@@ -92,6 +92,7 @@ int gen_step(tnt_decoder* D, const tnt_contexts* ctx1, const GenWs& g, int B, in
   tnt_embed_params e = {};
   e.ids = g.cur; e.table = D->table; e.pos_table = D->pos_table; e.out = g.f.X0; e.ldo = D->cfg.d; e.start_pos = g.pos;
   e.B = B; e.T = 1; e.d = D->cfg.d; e.n_pos = D->cfg.max_positions; e.pad_idx = D->cfg.pad_idx; e.dtype = D->cfg.dtype;
+  e.vocab = D->cfg.vocab; e.error_flags = D->err_flags;
   TNT_TRY(tnt_embed_fwd(&e, st));
   for (int l = 0; l < D->cfg.n_layers; ++l)
     TNT_TRY(run_layer(D, l, ctx1, g.f, g.f.X0, g.f.X0, B, 1, g.ring[l], g.pos, nullptr, false, st));
@@ -141,6 +142,7 @@ int gen_step_pointer(tnt_decoder* D, const tnt_contexts* ctx1, const PtrWs& w, c
   tnt_embed_params e = {};
   e.ids = g.cur; e.table = D->table; e.pos_table = D->pos_table; e.out = g.f.X0; e.ldo = d; e.start_pos = g.pos;
   e.B = B; e.T = 1; e.d = d; e.n_pos = D->cfg.max_positions; e.pad_idx = D->cfg.pad_idx; e.dtype = dt;
+  e.vocab = D->cfg.vocab; e.error_flags = D->err_flags;
   TNT_TRY(tnt_embed_fwd(&e, st));
   // inp_embed is kept as the left half of `cat` (the layers overwrite X0)
   TNT_CUDA(cudaMemcpy2DAsync(w.cat, 2 * d * E, g.f.X0, d * E, d * E, B, cudaMemcpyDeviceToDevice, st));

@@ -83,6 +83,7 @@ size_t plan(tnt_decoder* D, char* base) {
     D->emb_scratch = a.take(max_band * d * E);
   }
   D->fold_dev = static_cast<FoldJob*>(a.take(sizeof(FoldJob) * kMaxFoldJobs));
+  D->err_flags = static_cast<int*>(a.take(256));
   return a.off;
 }
 
@@ -231,6 +232,7 @@ extern "C" int tnt_decoder_load(tnt_decoder* d, const char* key, const float* da
 extern "C" int tnt_decoder_finalize(tnt_decoder* D, tnt_stream stream) {
   TNT_CHECK_ARG(D && D->wmem, "decoder_finalize: bind the weight memory first");
   const tnt_decoder_config& c = D->cfg;
+  if (!D->finalized) TNT_CUDA(cudaMemsetAsync(D->err_flags, 0, sizeof(int), as_stream(stream)));   // first finalize after bind
   Loader L{D, as_stream(stream)};
   const int d = c.d, ns = c.n_sources;
   for (int l = 0; l < c.n_layers; ++l) {

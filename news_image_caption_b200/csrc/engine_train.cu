@@ -407,7 +407,16 @@ int embed_bwd(Ctx& c, const int64_t* ids, int B, int T, TrainWs& w, const void* 
     TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.G, d, w.Hrows, di, gp, di, d, di, N, TNT_F32, nullptr, 0, cnt, sq));
     // d H [rows, dim_i] = sqrt(d) G . proj_i, scattered into the band table (padding row 0 skipped)
     TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.G, d, D->emb_proj[i], di, w.dH, di, N, di, d, c.dt, nullptr, 0, cnt, sq));
-    TNT_TRY(scatter_table_grad(w.dH, di, loc, cnt, N, gt, di, di, c.dt, c.st));
+    if (D->sparse_rows) {
+      // data-parallel training: the rows join the packed list the ranks all-gather (tnt_decoder_set_sparse_embed_grad); the
+      // dense band-table gradient then holds the softmax part only and is final at stage 0
+      TNT_CHECK_ARG(di == d && N <= D->sparse_capacity, "train: sparse embedding gradient needs band dim == d and capacity >= B*T");
+      TNT_TRY(pack_band_rows(w.dH, di, loc, w.band_cnt, i, nb, N, D->sparse_rows, d, D->sparse_meta, D->sparse_count, di, c.dt, c.st));
+      continue;
+    }
+    // every band is an nn.Embedding(band_size, dim, padding_idx): its LOCAL row padding_idx gets no gradient (adaptive.py:42)
+    const int skip = D->cfg.embed_padding_idx >= 0 ? D->cfg.embed_padding_idx : -1;
+    TNT_TRY(scatter_table_grad(w.dH, di, loc, cnt, N, gt, di, di, c.dt, skip, c.st));
   }
   return TNT_OK;
 }
@@ -430,6 +439,16 @@ extern "C" int tnt_decoder_set_dropout(tnt_decoder* d, const tnt_dropout_config*
   for (float p : ps) TNT_CHECK_ARG(p >= 0.f && p < 1.f, "decoder_set_dropout: probability %f outside [0, 1)", p);
   d->drop_cfg = c;
   d->drop_step = 0;
+  return TNT_OK;
+}
+
+extern "C" int tnt_decoder_set_sparse_embed_grad(tnt_decoder* d, void* rows, int64_t* meta, int* count, int capacity_rows) {
+  TNT_CHECK_ARG(d, "decoder_set_sparse_embed_grad: null decoder");
+  TNT_CHECK_ARG(!rows || (meta && count && capacity_rows > 0 && aligned16(rows)), "decoder_set_sparse_embed_grad: bad buffers");
+  d->sparse_rows = rows;
+  d->sparse_meta = reinterpret_cast<long long*>(meta);
+  d->sparse_count = count;
+  d->sparse_capacity = rows ? capacity_rows : 0;
   return TNT_OK;
 }
 

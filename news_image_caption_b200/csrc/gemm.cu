@@ -528,15 +528,13 @@ static int launch_tc_cg(const GemmArgs& g, int BN, cudaStream_t st) {
   const long tiles = static_cast<long>(g.groups) * ((g.M + tc::BM * CG - 1) / (tc::BM * CG)) * n_tiles;
   const int grid = CG * static_cast<int>(std::min<long>(tiles, num_sms() / CG));
   auto kern = tc::gemm_tc_kernel<EPI, TOut, CG>;
-  static bool attr_set = false;   // per instantiation
-  if (!attr_set) {
-    TNT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBudget + 4096));
-    attr_set = true;
-  }
+  static PerDeviceOnce attr_once;   // per instantiation and device
+  if (attr_once.first()) TNT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBudget + 4096));
   GemmArgs ga = g;
   ga.nacc = g_single_acc ? 1 : tc::acc_count(CG, BN);
   TNT_CUDA(launch_pdl(kern, dim3(grid), dim3(tc::kThreads), smem, st, CG, tmA, tmW, ga, BN, stages, n_tiles));
   TNT_LAUNCHED();
+  variant_hit(CG == 2 ? V_GEMM_TC_PAIR : V_GEMM_TC_1CTA);
   return TNT_OK;
 }
 
@@ -551,6 +549,7 @@ static int launch_simt(const GemmArgs& g, cudaStream_t st) {
   dim3 grid((g.N + simt::TN - 1) / simt::TN, (g.M + simt::TM - 1) / simt::TM, g.groups);
   simt::gemm_simt_kernel<EPI, TIn, TOut><<<grid, 256, 0, st>>>(g);
   TNT_LAUNCHED();
+  variant_hit(V_GEMM_SIMT);
   return TNT_OK;
 }
 
@@ -633,7 +632,10 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
       (epi == EPI_NONE || epi == EPI_RELU || epi == EPI_GLU || epi == EPI_RESIDUAL)) {
     int bn_s, S;
     const long pt = static_cast<long>((g.M + tc::BM * CG - 1) / (tc::BM * CG)) * ((g.N + BN - 1) / BN);
-    if (splitk_plan(g.M, g.N, g.K, pt, &bn_s, &S)) return launch_gemm_splitk(g, epi, p->dtype_out, bn_s, S, st);
+    if (splitk_plan(g.M, g.N, g.K, pt, &bn_s, &S)) {
+      variant_hit(V_GEMM_SPLITK);
+      return launch_gemm_splitk(g, epi, p->dtype_out, bn_s, S, st);
+    }
   }
   g.n_tiles = (g.N + BN - 1) / BN;
   if (n_tiles_out) *n_tiles_out = g.n_tiles;

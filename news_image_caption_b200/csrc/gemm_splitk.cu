@@ -229,11 +229,8 @@ static int launch_splitk_t(const GemmArgs& g, int BN, int S, cudaStream_t st) {
   const int smem = part_bytes + stages * stage_bytes + 1024 + 512 + 1024;
   const int tiles = ((g.M + sk::BM - 1) / sk::BM) * ((g.N + BN - 1) / BN);
   auto kern = sk::gemm_splitk_kernel<EPI, TOut>;
-  static bool attr_set = false;   // per instantiation
-  if (!attr_set) {
-    TNT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, sk::kSmemBudget + 4096));
-    attr_set = true;
-  }
+  static PerDeviceOnce attr_once;   // per instantiation and device
+  if (attr_once.first()) TNT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, sk::kSmemBudget + 4096));
   TNT_CUDA(launch_pdl(kern, dim3(tiles * S), dim3(sk::kThreads), smem, st, S, tmA, tmW, g, BN, stages, S));
   TNT_LAUNCHED();
   return TNT_OK;

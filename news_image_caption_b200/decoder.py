@@ -104,7 +104,7 @@ class DynamicConvDecoder(nn.Module):
     def __init__(self, decoder_output_dim=1024, decoder_attention_heads=16, decoder_ffn_embed_dim=4096,
                  decoder_kernel_size_list=(3, 7, 15, 31), vocab_size=50265, adaptive_softmax_cutoff=(5000, 20000),
                  sources=('image', 'article'), source_dim=None, padding_idx=1, max_positions=513,
-                 dtype=torch.bfloat16, device='cuda', init_std=None):
+                 dtype=torch.bfloat16, device='cuda', init_std=None, embed_padding_idx=0):
         super().__init__()
         self.d, self.heads, self.ffn = decoder_output_dim, decoder_attention_heads, decoder_ffn_embed_dim
         self.kernels = list(decoder_kernel_size_list)
@@ -114,6 +114,7 @@ class DynamicConvDecoder(nn.Module):
         self.source_dim = dict(DEFAULT_SOURCE_DIM)
         self.source_dim.update(source_dim or {})
         self.pad = padding_idx
+        self.embed_padding_idx = -1 if embed_padding_idx is None else int(embed_padding_idx)   # config.yaml:39 (adaptive.py:42)
         self.max_positions = max_positions
         self.dtype_code, self.torch_dtype = _dtype_code(dtype)
         shapes = reference_shapes(self.d, self.heads, self.ffn, self.kernels, self.vocab, self.cutoffs,
@@ -157,6 +158,7 @@ class DynamicConvDecoder(nn.Module):
         for i, v in enumerate(self.cutoffs):
             c.cutoffs[i] = v
         c.pad_idx, c.max_positions, c.dtype = self.pad, self.max_positions, self.dtype_code
+        c.embed_padding_idx = self.embed_padding_idx
         return c
 
     def prepare(self):
@@ -194,6 +196,18 @@ class DynamicConvDecoder(nn.Module):
                 _lib.lib().tnt_decoder_destroy(self._handle)
         except Exception:
             pass
+
+    def check_input_errors(self):
+        """Raises if a kernel of this decoder saw a token id outside [0, vocab) (nn.Embedding's IndexError in the
+        reference, adaptive.py:61-76) or a position beyond the sinusoid table.  Synchronises the current stream;
+        called wherever the mirror already synchronises (loss `.item()`, trimmed generation, host scoring)."""
+        flags = _lib.lib().tnt_decoder_error_flags(self._h(), _stream())
+        if flags < 0:
+            _lib.check(flags, 'tnt_decoder_error_flags')
+        if flags & 1:
+            raise IndexError('token id outside [0, %d) in the decoder input (the affected rows were written as NaN)' % self.vocab)
+        if flags & 2:
+            raise IndexError('position beyond the sinusoid table (max_positions=%d)' % self.max_positions)
 
     def _workspace(self, key, nbytes):
         t = self._ws.get(key)
@@ -292,6 +306,7 @@ class DynamicConvDecoder(nn.Module):
                    'tnt_decoder_generate')
         if trim:
             n = steps.value
+            self.check_input_errors()
             return lp[:, :n], ids[:, :n + 1]
         return lp, ids
 
@@ -343,11 +358,16 @@ class DynamicConvDecoder(nn.Module):
             mod._parameters[parts[-1]] = own[owner]
         named = [(k, p) for k, p in self.named_parameters() if 'token_embedder_position' not in k]
         # arena order = the order in which the backward pass finishes gradients (tnt_decoder_train_stages):
-        # softmax-only parameters, layers last -> first, embedding bands (tied output rows) last
+        # stage 0: softmax-only parameters AND the band tables (tied output rows) -- their dense softmax-side gradient is final
+        # there; the <= B*T embedding rows added when the backward ends are exchanged as a packed row list in data-parallel
+        # training (trainer.py; with the dense scatter the tables are final at the last stage) -- then layers last -> first,
+        # then the band projections
         n_layers = len(self.kernels)
+        self.band_tables_in_stage0 = True
 
         def stage_of(k):
-            if k.startswith('adaptive_softmax.'):
+            if k.startswith('adaptive_softmax.') or (k.startswith('embedder.token_embedder_adaptive.embeddings.') and
+                                                     k.endswith('.0.weight')):
                 return 0
             if k.startswith('layers.'):
                 return n_layers - int(k.split('.')[1])
@@ -379,18 +399,30 @@ class DynamicConvDecoder(nn.Module):
             _lib.check(L.tnt_decoder_set_grad(h, k.encode(), _ptr(p.grad)), 'tnt_decoder_set_grad ' + k)
         return self
 
+    def band_table_grads(self):
+        """fp32 gradient tensors of the vocabulary band tables, band order (views of `flat_grads`)."""
+        e = 'embedder.token_embedder_adaptive.embeddings.%d.0.weight'
+        own = dict(self.named_parameters())
+        return [own[e % i].grad for i in range(len(self.cutoffs))]
+
     def mark_updated(self):
         """Call after the optimizer changed the parameters: the prepared (folded, cast) weights are rebuilt."""
         self._dirty = True
 
     def set_dropout(self, dropout=0.0, input_dropout=0.0, weight_dropout=0.0, attention_dropout=0.0, relu_dropout=0.0,
-                    seed=0):
+                    seed=0, rank=None):
         """Dropout of `train_step` (the constructor arguments of DynamicConvDecoder, decoder_flattened.py:24-31;
         config.yaml:51-69).  Masks are counter based: step k after this call uses seed + k, and every mask bit can
         be reproduced with ops.dropout_bits(seed + k, site, index).  All zero switches dropout off (parity mode)."""
+        # data-parallel replicas must not drop the same positions on their different shards (the reference draws from a
+        # per-process RNG): the rank (default: torch.distributed's) is mixed into the seed; rank 0 keeps `seed` itself
+        if rank is None:
+            import torch.distributed as dist
+            rank = dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
+        seed = (int(seed) + int(rank) * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
         cfg = _lib.DropoutConfig()
         cfg.dropout, cfg.input_dropout, cfg.weight_dropout = dropout, input_dropout, weight_dropout
-        cfg.attention_dropout, cfg.relu_dropout, cfg.seed = attention_dropout, relu_dropout, int(seed)
+        cfg.attention_dropout, cfg.relu_dropout, cfg.seed = attention_dropout, relu_dropout, seed
         _lib.check(_lib.lib().tnt_decoder_set_dropout(self._h(), C.byref(cfg)), 'tnt_decoder_set_dropout')
 
     def train_step(self, prev_target, target, contexts, loss_scale=1.0):
@@ -436,6 +468,7 @@ class DynamicConvDecoder(nn.Module):
         _lib.check(L.tnt_decoder_score_host(h, _ptr(ids_host), _ptr(target_host), C.byref(c), _ptr(self._out2),
                                             _ptr(stg), stg.numel(), _ptr(ws), ws.numel(), _stream()),
                    'tnt_decoder_score_host')
+        self.check_input_errors()
         return float(self._out2[0]), float(self._out2[1])
 
     def _host_contexts(self, ids_host, contexts_host):
@@ -645,7 +678,9 @@ class AdaptiveLoss(nn.Module):
         if reduction != 'sum':
             raise NotImplementedError('reduction=%r' % reduction)
         out = decoder.nll(net_output[0], decoder_target)
-        return out[:1], int(out[1].item())
+        n = int(out[1].item())
+        decoder.check_input_errors()
+        return out[:1], n
 
 
 def sinusoid_table(n, d, padding_idx=1):

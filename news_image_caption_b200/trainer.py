@@ -2,10 +2,17 @@
 
 One process per GPU; every rank holds a full replica and a shard of the batch.  A step is
   engine forward + AdaptiveLoss + backward (tnt_decoder_train_step, all CUDA kernels of this repo)
-  -> sum all-reduce of the flat gradient arena, stage by stage, on a communication stream that overlaps the
-     rest of the backward pass (torch.distributed / NCCL over NVLink: the ONLY collective of the path,
-     SURVEY 8e) plus a 2-scalar all-reduce of (loss_sum, n_tokens): the reference normalises the loss by the
-     GLOBAL non-pad token count (criteria/adaptive_loss.py:62-65, transformer_faces_objects.py:85-88)
+  -> the gradient exchange (torch.distributed / NCCL over NVLink: the ONLY collective of the path),
+     stage by stage on a communication stream that overlaps the rest of the backward pass:
+       * every stage's slice of the flat fp32 gradient arena is cast to bf16 (tnt_cast), sum-all-reduced in bf16 -- half the
+         wire bytes of the fp32 arena -- and cast back into the fp32 arena BertAdam reads;
+       * the embedding bands are tied to the softmax output rows, so their dense (softmax-side) gradient is final at stage 0
+         and is exchanged FIRST, under the whole backward; the <= B*T embedding rows that only exist when the backward ends
+         travel as a packed row list (tnt_decoder_set_sparse_embed_grad: 4 MB per rank in bf16, one all-gather) that every
+         rank scatters into its table gradient (tnt_embed_grad_scatter) -- instead of a second, un-overlappable pass over
+         the 206 MB tables;
+       * a 2-scalar all-reduce of (loss_sum, n_tokens): the reference normalises the loss by the GLOBAL non-pad token count
+         (criteria/adaptive_loss.py:62-65, transformer_faces_objects.py:85-88)
   -> fused BertAdam over the flat arenas (tnt_bert_adam_step; config.yaml:126-136).
 torch supplies memory, streams and the process group only."""
 import ctypes as C
@@ -15,6 +22,7 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
+from ._lib import TNT_BF16, TNT_F32
 
 
 def warmup_linear(x, warmup):
@@ -24,22 +32,50 @@ def warmup_linear(x, warmup):
     return max((x - 1.0) / (warmup - 1.0), 0.0)
 
 
-class GradientExchange:
-    """Sum all-reduce of slices of one flat gradient buffer.  Pure torch.distributed plumbing: works with
-    CPU tensors over gloo (the world_size-2 CPU tests) and with CUDA tensors over NCCL."""
+def _cast(src, dst):
+    """dst <- src across fp32 / bf16 on the current stream: the library's own kernel on the GPU, torch on the CPU (gloo tests)."""
+    if src.is_cuda:
+        code = {torch.float32: TNT_F32, torch.bfloat16: TNT_BF16}
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        _lib.check(_lib.lib().tnt_cast(C.c_void_p(src.data_ptr()), C.c_void_p(dst.data_ptr()), src.numel(), code[src.dtype],
+                                       code[dst.dtype], st), 'tnt_cast')
+    else:
+        dst.copy_(src)
 
-    def __init__(self, flat_grads, slices, group=None):
+
+class GradientExchange:
+    """Sum all-reduce of slices of one flat fp32 gradient buffer, on the wire in `wire` precision ('bf16' halves the bytes;
+    'fp32' is exact).  Pure torch.distributed plumbing: works with CPU tensors over gloo (the world_size-2 CPU tests) and
+    with CUDA tensors over NCCL."""
+
+    def __init__(self, flat_grads, slices, group=None, wire='bf16'):
         self.flat, self.slices, self.group = flat_grads, [tuple(s) for s in slices], group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if wire not in ('bf16', 'fp32'):
+            raise ValueError('wire must be "bf16" or "fp32"')
+        self.wire = wire
+        self.wire_buf = torch.empty_like(flat_grads, dtype=torch.bfloat16) if (wire == 'bf16' and self.world > 1) else None
         self.pending = []
+
+    def bytes_on_wire(self):
+        n = sum(b - a for a, b in self.slices if a is not None and b > a)
+        return n * (2 if self.wire == 'bf16' else 4)
 
     def reduce_slice(self, i, async_op=True):
         a, b = self.slices[i]
         if self.world == 1 or a is None or b <= a:
             return
+        if self.wire_buf is not None:
+            _cast(self.flat[a:b], self.wire_buf[a:b])
+            w = dist.all_reduce(self.wire_buf[a:b], op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
+            if async_op:
+                self.pending.append((w, a, b))
+            else:
+                _cast(self.wire_buf[a:b], self.flat[a:b])
+            return
         w = dist.all_reduce(self.flat[a:b], op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
         if async_op:
-            self.pending.append(w)
+            self.pending.append((w, None, None))
 
     def reduce_scalars(self, t):
         if self.world > 1:
@@ -47,14 +83,61 @@ class GradientExchange:
         return t
 
     def finish(self):
-        for w in self.pending:
+        for w, a, b in self.pending:
             w.wait()
+            if a is not None:
+                _cast(self.wire_buf[a:b], self.flat[a:b])
         self.pending = []
+
+
+class SparseRowExchange:
+    """All-gather of every rank's packed embedding-gradient rows (rows [N, d] + meta [N] int64 + count, one byte buffer per
+    rank, one collective) and their scatter into the dense fp32 band-table gradients."""
+
+    def __init__(self, n_rows, d, dtype, device, group=None):
+        self.n, self.d, self.dtype, self.group = n_rows, d, dtype, group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        es = 2 if dtype == torch.bfloat16 else 4
+        self.rows_bytes, self.meta_bytes = n_rows * d * es, n_rows * 8
+        self.bytes = self.rows_bytes + self.meta_bytes + 64
+        self.mine = torch.zeros(self.bytes, dtype=torch.uint8, device=device)
+        self.all = torch.zeros(self.world * self.bytes, dtype=torch.uint8, device=device)
+
+    def views(self, buf):
+        rows = buf[:self.rows_bytes].view(self.dtype).view(self.n, self.d)
+        meta = buf[self.rows_bytes:self.rows_bytes + self.meta_bytes].view(torch.int64)
+        count = buf[self.rows_bytes + self.meta_bytes:self.rows_bytes + self.meta_bytes + 4].view(torch.int32)
+        return rows, meta, count
+
+    def gather(self, async_op=False):
+        if self.world == 1:
+            self.all.copy_(self.mine)
+            return None
+        return dist.all_gather_into_tensor(self.all, self.mine, group=self.group, async_op=async_op)
+
+    def scatter_into(self, band_grads, skip_row):
+        """band_grads: list of fp32 [rows_i, d] gradient tensors (views of the flat arena), one per vocabulary band."""
+        for r in range(self.world):
+            rows, meta, count = self.views(self.all[r * self.bytes:(r + 1) * self.bytes])
+            if rows.is_cuda:
+                ptrs = (C.c_void_p * len(band_grads))(*[g.data_ptr() for g in band_grads])
+                dims = (C.c_int * len(band_grads))(*[g.shape[1] for g in band_grads])
+                code = TNT_BF16 if self.dtype == torch.bfloat16 else TNT_F32
+                st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+                _lib.check(_lib.lib().tnt_embed_grad_scatter(C.c_void_p(rows.data_ptr()), self.d, C.c_void_p(meta.data_ptr()),
+                                                             C.c_void_p(count.data_ptr()), self.n, ptrs, dims, len(band_grads),
+                                                             skip_row, code, st), 'tnt_embed_grad_scatter')
+            else:                                   # CPU restatement of the kernel for the gloo tests
+                n = int(count[0])
+                band, loc = meta[:n] >> 32, meta[:n] & 0xffffffff
+                for i, g in enumerate(band_grads):
+                    m = (band == i) & (loc != skip_row)
+                    g.index_add_(0, loc[m], rows[:n][m].float())
 
 
 class Trainer:
     def __init__(self, decoder, lr=1e-4, betas=(0.9, 0.98), eps=1e-6, weight_decay=1e-5, max_grad_norm=0.1,
-                 warmup=0.05, t_total=-1, group=None, overlap=True):
+                 warmup=0.05, t_total=-1, group=None, overlap=True, wire='bf16', sparse_embed=True):
         self.dec = decoder.enable_training()
         self.lr, self.betas, self.eps, self.wd, self.max_norm = lr, betas, eps, weight_decay, max_grad_norm
         self.warmup, self.t_total, self.step_no = warmup, t_total, 0
@@ -68,38 +151,78 @@ class Trainer:
             seg[off // 64:(off + cnt + 63) // 64] = i
         self.seg_of_chunk = seg.cuda()
         self.seg_sq = torch.zeros(self.n_segments, dtype=torch.float32, device='cuda')
-        self.exchange = GradientExchange(self.dec.flat_grads, self.dec.stage_slices, group)
+        self.exchange = GradientExchange(self.dec.flat_grads, self.dec.stage_slices, group, wire=wire)
+        self.group = group
         self.comm_stream = torch.cuda.Stream() if self.exchange.world > 1 else None
         self.gscale = torch.ones(1, dtype=torch.float32, device='cuda')
+        # multi-GPU: the embedding rows of the tied band tables travel as a packed list (the arena keeps the band tables in
+        # stage 0, where their dense softmax part is final); a band whose dim differs from d keeps the dense path
+        self.sparse = None
+        self.sparse_embed = bool(sparse_embed and self.exchange.world > 1 and self.dec.band_tables_in_stage0)
+
+    def exchange_description(self):
+        ex = self.exchange
+        return ('%s sum all-reduce of the %.0f MB flat gradient arena in %d stages on a comm stream (%s wire, %.0f MB per step)%s '
+                '+ 2-scalar all-reduce (loss_sum, n_tokens); world %d' % (
+                    'NCCL' if self.dec.flat_grads.is_cuda else 'gloo', self.dec.flat_grads.numel() * 4 / 1e6, len(ex.slices), ex.wire,
+                    ex.bytes_on_wire() / 1e6,
+                    ' + all-gather of the packed embedding-row gradients (%.1f MB per rank)' % (self.sparse.bytes / 1e6) if self.sparse else '',
+                    ex.world))
 
     def lr_now(self):
         if self.t_total > 0:
             return self.lr * warmup_linear(self.step_no / self.t_total, self.warmup)
         return self.lr
 
+    def _ensure_sparse(self, n_rows):
+        if not self.sparse_embed:
+            return
+        if self.sparse is None or self.sparse.n != n_rows:
+            dec = self.dec
+            self.sparse = SparseRowExchange(n_rows, dec.d, dec.torch_dtype, 'cuda', self.group)
+            rows, meta, count = self.sparse.views(self.sparse.mine)
+            _lib.check(_lib.lib().tnt_decoder_set_sparse_embed_grad(dec._h(), C.c_void_p(rows.data_ptr()), C.c_void_p(meta.data_ptr()),
+                                                                    C.c_void_p(count.data_ptr()), n_rows),
+                       'tnt_decoder_set_sparse_embed_grad')
+
     def step(self, prev_target, target, contexts):
         """One optimisation step on this rank's shard.  Returns the GLOBAL [loss_sum (nats), n_tokens] tensor
         (device); the reported loss of the reference is loss_sum / n_tokens / ln 2 (bits per token)."""
         dec, L = self.dec, _lib.lib()
+        ids = prev_target['roberta'] if isinstance(prev_target, dict) else prev_target
+        self._ensure_sparse(ids.shape[0] * ids.shape[1])
         out = dec.train_step(prev_target, target, contexts, loss_scale=1.0)
         cur = torch.cuda.current_stream()
         if self.exchange.world > 1:
             h = dec._h()
             n_stages = L.tnt_decoder_train_stages(h)
+            if not self.sparse_embed and dec.band_tables_in_stage0:
+                # dense embedding scatter: the band tables (arena stage 0) are only final when the backward ends
+                order = list(range(1, n_stages)) + [0]
+                wait_on = {0: n_stages - 1}
+            else:
+                order, wait_on = list(range(n_stages)), {}
             if self.overlap:
                 with torch.cuda.stream(self.comm_stream):
-                    for s in range(n_stages):
-                        _lib.check(L.tnt_decoder_stream_wait_stage(h, s, C.c_void_p(self.comm_stream.cuda_stream)),
+                    for s in order:
+                        _lib.check(L.tnt_decoder_stream_wait_stage(h, wait_on.get(s, s), C.c_void_p(self.comm_stream.cuda_stream)),
                                    'tnt_decoder_stream_wait_stage')
                         self.exchange.reduce_slice(s)
+                    if self.sparse is not None:
+                        self.sparse.gather()
                     self.exchange.finish()
                 cur.wait_stream(self.comm_stream)
             else:
-                for s in range(n_stages):
+                for s in order:
                     self.exchange.reduce_slice(s, async_op=False)
+                if self.sparse is not None:
+                    self.sparse.gather()
+            if self.sparse is not None:
+                self.sparse.scatter_into(dec.band_table_grads(), dec.embed_padding_idx)
             self.exchange.reduce_scalars(out)
         # gradient of the reference loss (sum-NLL / n_tokens / ln 2): scale by the global token count on the device
-        torch.reciprocal(out[1:2] * math.log(2.0), out=self.gscale)
+        # (an all-padding global batch has n_tokens == 0: every gradient is 0 then, keep the scale finite)
+        torch.reciprocal(out[1:2].clamp_min(1.0) * math.log(2.0), out=self.gscale)
         a = _lib.AdamParams()
         a.params, a.grads, a.m, a.v = dec.flat_params.data_ptr(), dec.flat_grads.data_ptr(), self.m.data_ptr(), self.v.data_ptr()
         a.n = dec.flat_params.numel()

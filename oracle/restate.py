@@ -293,7 +293,7 @@ def embed(ids: torch.Tensor, sd: SD, cutoffs: Sequence[int], start_pos: int = 0,
     positional.py:167-211, 231-268; sum -- sum_text_field_embedder.py:117."""
     B, T = ids.shape
     d = sd[p + 'token_embedder_adaptive.embeddings.0.1.weight'].shape[0]
-    out = torch.zeros(B, T, d)
+    out = torch.zeros(B, T, d, device=ids.device)       # device-agnostic: bench.py also runs this on CUDA tensors (eager comparator)
     lo = 0
     for i, hi in enumerate(cutoffs):
         m = (ids >= lo) & (ids < hi)
@@ -305,7 +305,7 @@ def embed(ids: torch.Tensor, sd: SD, cutoffs: Sequence[int], start_pos: int = 0,
         lo = hi
     out = out * math.sqrt(d)
     tab = sd[p + 'token_embedder_position.weights']
-    pos = torch.arange(T)[None, :].expand(B, T) + 2 + start_pos
+    pos = torch.arange(T, device=ids.device)[None, :].expand(B, T) + 2 + start_pos
     pos = torch.where(ids == 1, torch.ones_like(pos), pos)
     return out + tab[pos]
 

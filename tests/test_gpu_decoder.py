@@ -221,9 +221,13 @@ def test_full_size_bf16_vs_oracle(full_model):
     loss_o, n_o = O.adaptive_nll(Xo, tgt, sd, cfg['cutoffs'])
     dec = make_decoder(cfg, sd, torch.bfloat16)
     X, _ = dec(prev.cuda(), cuda_ctx(ctx))
-    assert rel_err(X, Xo) < 2e-2 * 4          # max-norm over 131k elements of a 4-layer bf16 stack
+    # north_star bounds logits and loss (2e-2 relative in bf16): the full-vocabulary log-probs are compared ROW-WISE at that
+    # tolerance; the hidden states in relative L2 (a max-norm over 131k elements of a 4-layer bf16 stack is not a logit bound)
     err = (X.float().cpu() - Xo).norm() / Xo.norm()
     assert err.item() < 2e-2
+    lp = dec.get_normalized_probs((X, None)).cpu()
+    lpo = O.adaptive_log_prob(Xo, sd, cfg['cutoffs'])
+    assert ((lp - lpo).abs().amax(-1) / lpo.abs().amax(-1)).max().item() < 2e-2
     out = dec.nll(X, tgt.cuda())
     assert abs(out[0].item() - loss_o.item()) < 2e-2 * abs(loss_o.item())
 

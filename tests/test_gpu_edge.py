@@ -119,3 +119,26 @@ def test_boundary_errors_are_loud():
         _lib.check(rc, 'tnt_decoder_forward')
     rc = L.tnt_decoder_forward(h, None, C.byref(c), X.data_ptr(), None, ws.data_ptr(), ws.numel(), None)
     assert rc != 0
+
+
+def test_out_of_range_token_id_is_loud():
+    """nn.Embedding raises IndexError for an id outside [0, vocab) (adaptive.py:61-76).  The engine never reads outside
+    its table: the offending row is written as NaN, a device error flag is raised and the mirror turns it into an
+    IndexError wherever it synchronises (loss .item(), trimmed generation); the flag clears on read."""
+    from news_image_caption_b200 import AdaptiveLoss
+    dec, sd = make(torch.bfloat16)
+    prev, tgt, ctx = synth.make_batch(3, 4, V, seed=59, S_img=3, S_art=9)
+    cc = {k: v.cuda() for k, v in ctx.items()}
+    bad = prev.clone()
+    bad[1, 2] = V + 7
+    X, _ = dec(bad.cuda(), cc)
+    assert torch.isnan(X[1].float()).any() and torch.isfinite(X[0].float()).all()
+    with pytest.raises(IndexError):
+        AdaptiveLoss(1)(dec, (X, None), tgt.cuda())
+    bad[1, 2] = -3
+    dec(bad.cuda(), cc)
+    with pytest.raises(IndexError):
+        dec.check_input_errors()
+    X, _ = dec(prev.cuda(), cc)                                       # a clean batch afterwards is clean
+    loss, n = AdaptiveLoss(1)(dec, (X, None), tgt.cuda())
+    assert torch.isfinite(loss).all() and n == int((tgt != 1).sum())

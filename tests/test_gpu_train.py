@@ -363,3 +363,42 @@ def test_train_step_full_width_bf16():
     worst = sorted(((l2_err(p.grad, sd[k].grad), k) for k, p in dec.named_parameters()
                     if 'token_embedder_position' not in k), reverse=True)
     assert worst[0][0] < 1e-1, '\n'.join('%.3e %s' % w for w in worst[:10])
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_sparse_embedding_gradient_equals_dense_scatter(dtype):
+    """Data-parallel form of the tied band-table gradient (tnt_decoder_set_sparse_embed_grad + tnt_embed_grad_scatter,
+    trainer.SparseRowExchange): the step packs the <= B*T embedding rows into a list instead of scattering them; the dense
+    tables then hold the softmax part only.  Scattering the list afterwards must reproduce the dense-mode gradients
+    (every other gradient is untouched), incl. the skipped band-local padding row."""
+    import ctypes as C
+    from news_image_caption_b200 import _lib
+    from news_image_caption_b200.trainer import SparseRowExchange
+    f = torch.load(os.path.join(G, 'tell2_small.pt'), weights_only=False)
+    cfg = f['config']
+    dec = make_decoder(cfg, f['state_dict'], dtype).enable_training()
+    prev, tgt = f['prev'].clone(), f['target'].cuda()
+    prev[0, 1] = 0                          # band-local row 0 of band 0 (the padding row) appears as an input id
+    prev[1, 2] = cfg['cutoffs'][0]          # ... and of band 1
+    ctx = {k: v.cuda() for k, v in f['contexts'].items()}
+    dec.train_step(prev.cuda(), tgt, ctx)
+    dense = dec.flat_grads.clone()
+    n = prev.numel()
+    sx = SparseRowExchange(n, cfg['d'], dec.torch_dtype, 'cuda')
+    rows, meta, count = sx.views(sx.mine)
+    L = _lib.lib()
+    _lib.check(L.tnt_decoder_set_sparse_embed_grad(dec._h(), C.c_void_p(rows.data_ptr()), C.c_void_p(meta.data_ptr()),
+                                                   C.c_void_p(count.data_ptr()), n), 'set_sparse')
+    dec.train_step(prev.cuda(), tgt, ctx)
+    assert int(count[0].item()) == n                       # every token lives in exactly one band
+    sparse_only = dec.flat_grads.clone()
+    tabs = dec.band_table_grads()
+    assert not torch.equal(sparse_only, dense)             # the rows really were withheld
+    sx.gather()
+    sx.scatter_into(tabs, dec.embed_padding_idx)
+    torch.cuda.synchronize()
+    assert rel_err(dec.flat_grads, dense) < (1e-5 if dtype == torch.float32 else 1e-2)
+    # back to the dense scatter
+    _lib.check(L.tnt_decoder_set_sparse_embed_grad(dec._h(), None, None, None, 0), 'set_sparse off')
+    dec.train_step(prev.cuda(), tgt, ctx)
+    assert rel_err(dec.flat_grads, dense) < 1e-5

@@ -1,0 +1,64 @@
+"""Multi-GPU check of the data-parallel training step (run under torchrun on N GPUs):
+N ranks x B captions with the bf16-wire staged all-reduce + the packed embedding-row all-gather (trainer.Trainer) must end
+with the same parameters as ONE process stepping on the concatenated N*B batch (fp32 engine: 1e-3; the wire is bf16).
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/check_dp_train.py
+"""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from news_image_caption_b200 import DynamicConvDecoder  # noqa: E402
+from news_image_caption_b200.decoder import random_state_dict  # noqa: E402
+from news_image_caption_b200.trainer import Trainer  # noqa: E402
+from oracle import synth  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ['RANK']), int(os.environ['WORLD_SIZE']), int(os.environ['LOCAL_RANK'])
+    torch.cuda.set_device(local)
+    dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    d, H, V, cut, B, T = 256, 4, 900, [300, 600, 900], 6, 9
+    kw = dict(decoder_output_dim=d, decoder_attention_heads=H, decoder_ffn_embed_dim=512, decoder_kernel_size_list=[3, 7],
+              vocab_size=V, adaptive_softmax_cutoff=cut[:-1])
+    sd = random_state_dict(d=d, heads=H, ffn=512, kernels=(3, 7), vocab=V, cutoffs=cut, seed=11)
+    prev, tgt, ctx = synth.make_batch(B * world, T, V, ('image', 'article'), seed=5, S_img=7, S_art=40)
+    cu = lambda c: {k: v.cuda() for k, v in c.items()}
+    results = {}
+    for wire, sparse in (('fp32', False), ('bf16', False), ('bf16', True), ('fp32', True)):
+        for dtype in (torch.float32,):
+            dec = DynamicConvDecoder(dtype=dtype, **kw).load_reference_state_dict(sd)
+            tr = Trainer(dec, lr=1e-2, max_grad_norm=0.1, weight_decay=1e-3, wire=wire, sparse_embed=sparse)
+            sl = slice(rank * B, (rank + 1) * B)
+            c = {k: (v[sl] if k.endswith('_mask') else v[:, sl]).contiguous() for k, v in ctx.items()}
+            for _ in range(3):
+                out = tr.step(prev[sl].cuda(), tgt[sl].cuda(), cu(c))
+            torch.cuda.synchronize()
+            results[(wire, sparse)] = (dec.flat_params.clone(), out.clone())
+    # single-process reference on the concatenated batch, run on every rank (the exchange is switched off: world forced to 1)
+    ref = DynamicConvDecoder(dtype=torch.float32, **kw).load_reference_state_dict(sd)
+    tr1 = Trainer(ref, lr=1e-2, max_grad_norm=0.1, weight_decay=1e-3)
+    tr1.exchange.world = 1
+    tr1.sparse_embed = False
+    for _ in range(3):
+        out1 = tr1.step(prev.cuda(), tgt.cuda(), cu(ctx))
+    torch.cuda.synchronize()
+    ok = True
+    for key, (p, out) in results.items():
+        err = ((p - ref.flat_params).abs().max() / ref.flat_params.abs().max()).item()
+        lerr = abs(out[0].item() - out1[0].item()) / abs(out1[0].item())
+        tol = 1e-4 if key[0] == 'fp32' else 2e-3
+        good = err < tol and lerr < 1e-3 and out[1].item() == out1[1].item()
+        ok = ok and good
+        if rank == 0:
+            print('wire=%s sparse_embed=%s: params rel err %.2e (tol %.0e), loss rel err %.2e, tokens %d/%d -> %s' % (
+                key[0], key[1], err, tol, lerr, out[1].item(), out1[1].item(), 'OK' if good else 'FAIL'))
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == '__main__':
+    main()
