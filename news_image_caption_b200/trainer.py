@@ -66,12 +66,14 @@ class GradientExchange:
         if self.world == 1 or a is None or b <= a:
             return
         if self.wire_buf is not None:
+            # cast -> all-reduce -> cast back, all in order on the calling (communication) stream: the next stage only
+            # becomes ready ~1 ms later, so nothing queues up, and only the LAST stage's 3 small ops trail the backward
+            # (deferring the cast-backs to finish() left 0.19 ms of them serialised after the last collective)
             _cast(self.flat[a:b], self.wire_buf[a:b])
             w = dist.all_reduce(self.wire_buf[a:b], op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
             if async_op:
-                self.pending.append((w, a, b))
-            else:
-                _cast(self.wire_buf[a:b], self.flat[a:b])
+                w.wait()                # stream-side wait (NCCL) / host wait (gloo)
+            _cast(self.wire_buf[a:b], self.flat[a:b])
             return
         w = dist.all_reduce(self.flat[a:b], op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
         if async_op:
@@ -85,8 +87,6 @@ class GradientExchange:
     def finish(self):
         for w, a, b in self.pending:
             w.wait()
-            if a is not None:
-                _cast(self.wire_buf[a:b], self.flat[a:b])
         self.pending = []
 
 

@@ -301,7 +301,7 @@ def embed(ids: torch.Tensor, sd: SD, cutoffs: Sequence[int], start_pos: int = 0,
             e = sd[p + 'token_embedder_adaptive.embeddings.%d.0.weight' % i]
             pr = sd[p + 'token_embedder_adaptive.embeddings.%d.1.weight' % i]
             # nn.Embedding(padding_idx=0): band-local row 0 receives no gradient from this path (adaptive.py:42,51)
-            out[m] = F.linear(F.embedding(ids[m] - lo, e, padding_idx=0), pr)
+            out[m] = F.linear(F.embedding(ids[m] - lo, e, padding_idx=0), pr).to(out.dtype)   # (.to: a no-op except under autocast)
         lo = hi
     out = out * math.sqrt(d)
     tab = sd[p + 'token_embedder_position.weights']

@@ -122,7 +122,7 @@ def test_c2_forward_B64_sampled_rows(models, need_attn):
     v = _forward_case(models, '2src', 64, need_attn)
     assert v['gemm.tc.pair'] >= 2            # the image and article K/V projections take the cta_group::2 kernel at this size
     assert v['gemm.simt'] == 0 and v['xattn.simt'] == 0, v      # no fp32 SIMT fallback anywhere in the default bf16 path
-    assert v['xattn.tc'] == 8 and v['xattn.tc.tileskip'] == 4   # 4 layers x 2 sources; the article source skips padding tiles
+    assert v['xattn.tc'] == 8 and v['xattn.tc.tileskip'] == 8   # 4 layers x 2 sources, both carry a key-padding mask: live-tile lists on
     assert v['xattn.tc.weights'] == (1 if need_attn else 0)     # the last layer's article attention returns its weights
     assert v['dynconv.fwd.tc'] == 4 and v['dynconv.fwd.simt'] == 0
 

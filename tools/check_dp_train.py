@@ -1,6 +1,6 @@
 """Multi-GPU check of the data-parallel training step (run under torchrun on N GPUs):
 N ranks x B captions with the bf16-wire staged all-reduce + the packed embedding-row all-gather (trainer.Trainer) must end
-with the same parameters as ONE process stepping on the concatenated N*B batch (fp32 engine: 1e-3; the wire is bf16).
+with the same parameters as ONE process stepping on the concatenated N*B batch (fp32 wire: 1e-4; bf16 wire: 2e-2 -- three Adam steps of lr 1e-2).
   python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/check_dp_train.py
 """
 import os
@@ -49,7 +49,7 @@ def main():
     for key, (p, out) in results.items():
         err = ((p - ref.flat_params).abs().max() / ref.flat_params.abs().max()).item()
         lerr = abs(out[0].item() - out1[0].item()) / abs(out1[0].item())
-        tol = 1e-4 if key[0] == 'fp32' else 2e-3
+        tol = 1e-4 if key[0] == 'fp32' else 2e-2     # bf16 wire: a parameter whose true gradient is ~0 takes Adam's +-lr step on rounding noise
         good = err < tol and lerr < 1e-3 and out[1].item() == out1[1].item()
         ok = ok and good
         if rank == 0:
