@@ -392,6 +392,23 @@ size_t tnt_decoder_loss_workspace_bytes(const tnt_decoder* d, int n_rows);
  * such a source (decoder_entity_pointer.py:326-334 overwrites attn last), else "article" (decoder_flattened.py:325) */
 int tnt_decoder_forward(tnt_decoder* d, const int64_t* ids, const tnt_contexts* ctx, void* X_out,
                         float* attn_out, void* workspace, size_t workspace_bytes, tnt_stream stream);
+/* Step-wise protocol -- `decoder(prev_target, contexts, incremental_state)` as the reference's own `_generate` loop drives
+ * it (transformer_flattened.py:250-275, decoder_flattened.py:96-146, 202-207).  The CALLER owns all state (the mirror keeps
+ * it in the incremental_state dict under the reference's "{Class}.{id}.{key}" names, utils/state.py:17-26, so
+ * filter_incremental_state / reorder_incremental_state keep working):
+ *   kv[s]      projected K / V of source s for all layers, [S+2, B, L*2d] engine dtype (tnt_decoder_kv_cache_bytes),
+ *              filled once by tnt_decoder_project_kv (the reference re-projects the memories in every step);
+ *   start_pos  tokens already consumed (SinusoidalPositionalEmbedding's `position`, positional.py:170-176);
+ *   hist_in[l] the last hist_len[l] (<= K_l - 1) conv inputs of layer l, [hist_len, B, d] oldest first
+ *              (`DynamicConv1dTBC.<id>.input_buffer`, dynamic.py:95-99); NULL / 0 before the first step;
+ *   hist_out[l] receives the updated buffer: the last min(K_l - 1, hist_len[l] + T) rows (must not alias hist_in[l]).
+ * ids [B, T] are the NEW tokens only; X_out [B, T, d]; attn_out optional [B, T, S_w + 2] as in tnt_decoder_forward. */
+size_t tnt_decoder_kv_cache_bytes(const tnt_decoder* d, int B, int S);
+int tnt_decoder_project_kv(tnt_decoder* d, const tnt_contexts* ctx, void* const* kv_out, tnt_stream stream);
+size_t tnt_decoder_incremental_workspace_bytes(const tnt_decoder* d, int B, int T, const int* S);
+int tnt_decoder_forward_incremental(tnt_decoder* d, const int64_t* ids, const tnt_contexts* ctx, void* const* kv, int start_pos,
+                                    const void* const* hist_in, const int* hist_len, void* const* hist_out, void* X_out,
+                                    float* attn_out, void* workspace, size_t workspace_bytes, tnt_stream stream);
 /* AdaptiveLoss(reduction='sum'): out[0] = loss sum (nats), out[1] = number of non-pad targets */
 int tnt_decoder_nll(tnt_decoder* d, const void* X, const int64_t* target, int n_rows, float* out2,
                     void* workspace, size_t workspace_bytes, tnt_stream stream);
@@ -491,6 +508,16 @@ int tnt_decoder_train_step(tnt_decoder* d, const int64_t* ids, const int64_t* ta
                            float loss_scale, float* out2, void* workspace, size_t workspace_bytes,
                            tnt_stream stream);
 
+/* The same step as two calls, for callers whose forward and loss are separate module calls -- the reference model runs
+ * `decoder(...)`, then `criterion(...)`, then the trainer's `loss.backward()` (transformer_faces_objects.py:79-88,
+ * callback_apex_trainer.py:229-233); the mirror's autograd Functions sit on these.  train_forward keeps every activation
+ * in `workspace` (tnt_decoder_train_workspace_bytes) and copies X [B, T, d] out; train_backward -- same ids / contexts /
+ * workspace, untouched in between -- computes the loss and all gradients exactly as tnt_decoder_train_step does. */
+int tnt_decoder_train_forward(tnt_decoder* d, const int64_t* ids, const tnt_contexts* ctx, void* X_out, void* workspace,
+                              size_t workspace_bytes, tnt_stream stream);
+int tnt_decoder_train_backward(tnt_decoder* d, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,
+                               float loss_scale, float* out2, void* workspace, size_t workspace_bytes, tnt_stream stream);
+
 /* Overlapping the gradient exchange with the backward pass: the step completes its gradients in stages --
  * stage 0: softmax-only parameters (class_proj, tail projections); stage 1+i: every parameter of layer
  * (n_layers-1-i); last stage: the embedding bands (tied output rows).  After tnt_decoder_train_step has been
@@ -525,6 +552,17 @@ typedef struct {
   float max_grad_norm, lr, beta1, beta2, eps, weight_decay;
 } tnt_adam_params;
 int tnt_bert_adam_step(const tnt_adam_params* p, tnt_stream stream);
+
+/* torch.optim.Adam over flat fp32 arenas -- the optimizer of the final* scripts: Adam(betas=(0.9, 0.98), eps=1e-9) driven by
+ * the Noam schedule rate(step) = factor * d_model^-0.5 * min(step^-0.5, step * warmup^-1.5)
+ * (final_roberta2/custom_v4.py:421-430, 491-498; the schedule itself is host arithmetic).  g' = scale * g + wd * p,
+ * bias-corrected moments at 1-based `step`: p -= lr / (1 - b1^step) * m / (sqrt(v) / sqrt(1 - b2^step) + eps). */
+int tnt_adam_step(float* params, const float* grads, float* m, float* v, int64_t n, const float* grad_scale_dev,
+                  float grad_scale, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                  tnt_stream stream);
+/* dst += alpha * (*alpha_dev) * src over n (multiple of 4) floats: how the mirror's autograd Functions add the fused engine
+ * backward (computed for an upstream gradient of 1) into `.grad`, scaled by the upstream gradient autograd hands them. */
+int tnt_grad_accumulate(float* dst, const float* src, int64_t n, float alpha, const float* alpha_dev, tnt_stream stream);
 
 /* End-to-end convenience used for the e2e benchmark: ids/targets/contexts/masks in PINNED HOST
  * memory, loss read back; performs the H2D copies, forward, loss and D2H on `stream` and

@@ -175,6 +175,11 @@ _SIGS = {
     'tnt_decoder_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
     'tnt_decoder_loss_workspace_bytes': (C.c_size_t, [vp, i32]),
     'tnt_decoder_forward': (i32, [vp, vp, C.POINTER(Contexts), vp, vp, vp, C.c_size_t, vp]),
+    'tnt_decoder_kv_cache_bytes': (C.c_size_t, [vp, i32, i32]),
+    'tnt_decoder_project_kv': (i32, [vp, C.POINTER(Contexts), C.POINTER(vp), vp]),
+    'tnt_decoder_incremental_workspace_bytes': (C.c_size_t, [vp, i32, i32, C.POINTER(i32)]),
+    'tnt_decoder_forward_incremental': (i32, [vp, vp, C.POINTER(Contexts), C.POINTER(vp), i32, C.POINTER(vp), C.POINTER(i32),
+                                              C.POINTER(vp), vp, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_nll': (i32, [vp, vp, vp, i32, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_log_prob': (i32, [vp, vp, i32, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_embed': (i32, [vp, vp, i32, i32, vp, vp]),
@@ -200,9 +205,13 @@ _SIGS = {
     'tnt_decoder_set_sparse_embed_grad': (i32, [vp, vp, vp, vp, i32]),
     'tnt_embed_grad_scatter': (i32, [vp, i64, vp, vp, i32, C.POINTER(vp), C.POINTER(i32), i32, i32, i32, vp]),
     'tnt_decoder_train_step': (i32, [vp, vp, vp, C.POINTER(Contexts), f32, vp, vp, C.c_size_t, vp]),
+    'tnt_decoder_train_forward': (i32, [vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp]),
+    'tnt_decoder_train_backward': (i32, [vp, vp, vp, C.POINTER(Contexts), f32, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_train_stages': (i32, [vp]),
     'tnt_decoder_stream_wait_stage': (i32, [vp, i32, vp]),
     'tnt_bert_adam_step': (i32, [C.POINTER(AdamParams), vp]),
+    'tnt_adam_step': (i32, [vp, vp, vp, vp, i64, vp, f32, f32, f32, f32, f32, f32, i32, vp]),
+    'tnt_grad_accumulate': (i32, [vp, vp, i64, f32, vp, vp]),
     'tnt_debug_force_simt_gemm': (None, [i32]),
     'tnt_debug_gemm_cta_group': (None, [i32]),
     'tnt_debug_pdl': (None, [i32]),

@@ -65,6 +65,7 @@ struct tnt_decoder {
   int article_idx = -1;   // source whose head-averaged attention the forward returns ("entity" if present, else "article")
   tnt_dropout_config drop_cfg = {};    // training dropout (tnt_decoder_set_dropout); all zero = off
   uint64_t drop_step = 0;              // training steps issued since the configuration was set
+  tnt_dropout_config pending_drc = {}; bool pending_dr_on = false; void* pending_ws = nullptr;   // train_forward -> train_backward
   // pipelined host scoring (tnt_decoder_score_host_submit / _wait): copy stream + per-slot events
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_h2d[2] = {}, ev_free[2] = {}, ev_done[2] = {};
@@ -102,10 +103,15 @@ FwdWs carve_fwd(const tnt_decoder* d, int B, int T, const int* S, void* ws, bool
 
 int embed(tnt_decoder* d, const int64_t* ids, int B, int T, void* out, const int* start_pos, cudaStream_t st);
 int project_kv(tnt_decoder* d, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st, bool decode_order = false);
-// one decoder layer on N = T*B rows; `ring`/`pos` != NULL selects the single-step conv (T must be 1)
+// caller-owned chronological conv history of one layer (the reference's `DynamicConv1dTBC.<id>.input_buffer`,
+// dynamic.py:95-99): `in` = the last `len` (<= K-1) conv inputs [len, B, C], oldest first; `out` (optional, must not
+// alias `in`) receives the last min(K-1, len + T) rows of [in ; this call's conv inputs]
+struct ConvHist { const void* in; int len; void* out; };
+// one decoder layer on N = T*B rows; `ring`/`pos` != NULL selects the single-step conv (T must be 1); `ch` the
+// step-wise protocol with caller-owned history (tnt_decoder_forward_incremental)
 int run_layer(tnt_decoder* d, int l, const tnt_contexts* ctx, const FwdWs& w, const void* Xin, void* Xout, int B, int T,
               void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st, int kv_group = 1,
-              const tnt_dropout_config* dr = nullptr);
+              const tnt_dropout_config* dr = nullptr, const ConvHist* ch = nullptr);
 // dr != NULL (training): the dropout sites of the layer are active with seed dr->seed (include/tnt_b200.h, TNT_DROP_SITE)
 int dropout_apply(const void* in, long ldi, const void* res, long ldr, void* out, long ldo, int rows, int cols, int dtype,
                   const tnt_dropout& dr, cudaStream_t st);

@@ -122,7 +122,7 @@ int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStre
 
 int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, const void* Xin, void* Xout, int B, int T,
               void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st, int kv_group,
-              const tnt_dropout_config* dr) {
+              const tnt_dropout_config* dr, const ConvHist* ch) {
   const tnt_decoder_config& c = D->cfg;
   const LayerW& L = D->layers[l];
   const int d = c.d, ns = c.n_sources, N = B * T, H = c.heads, dt = c.dtype;
@@ -159,7 +159,21 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     cp.x = w.h; cp.ldx = d; cp.logits = w.logits; cp.ldl = ldl; cp.y = w.cbuf; cp.ldy = d;
     cp.T = T; cp.B = B; cp.C = d; cp.H = H; cp.K = L.K; cp.dtype = dt;
     cp.drop = drop_site(dr, dr ? dr->weight_dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_TAPS));
+    if (ch && ch->len > 0) {
+      TNT_CHECK_ARG(ch->in && ch->len <= L.K - 1, "decoder: conv history of layer %d has %d rows (K = %d)", l, ch->len, L.K);
+      cp.hist = ch->in;
+      cp.hist_len = ch->len;
+    }
     TNT_TRY(tnt_dynconv_fwd(&cp, st));
+    if (ch && ch->out && L.K > 1) {      // new history = last min(K-1, len + T) rows of [history ; this call's conv inputs]
+      const int keep = std::min(L.K - 1, ch->len + T), from_x = std::min(T, keep), from_h = keep - from_x;
+      const size_t row = static_cast<size_t>(B) * d * E;
+      if (from_h > 0)
+        TNT_CUDA(cudaMemcpyAsync(ch->out, static_cast<const char*>(ch->in) + static_cast<size_t>(ch->len - from_h) * row, from_h * row,
+                                 cudaMemcpyDeviceToDevice, st));
+      TNT_CUDA(cudaMemcpyAsync(static_cast<char*>(ch->out) + from_h * row, static_cast<const char*>(w.h) + static_cast<size_t>(T - from_x) * row,
+                               from_x * row, cudaMemcpyDeviceToDevice, st));
+    }
   }
   TNT_TRY(linear(w.cbuf, d, L.w2, d, L.b2, w.ybuf, d, N, d, d, dt, EPI_RESIDUAL, Xin, d, st, 1, 0, 0, 0, 0, 0, L.wq, ns * dd, &d_conv));
   TNT_TRY(layernorm(w.ybuf, w.X1, d, L.ln_conv_g, L.ln_conv_b, N, d, 1, dt, 0, 0, st));
@@ -279,6 +293,71 @@ extern "C" int tnt_decoder_forward(tnt_decoder* D, const int64_t* ids, const tnt
     // Xin == w.X0 is safe: X0 is only overwritten by context_fc after its last use as residual.
     void* out = last ? X_out : w.X0;
     TNT_TRY(run_layer(D, l, ctx, w, cur, out, B, T, nullptr, nullptr, last ? attn_out : nullptr, last, st));
+    cur = out;
+  }
+  return TNT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Step-wise protocol of the reference (`forward(prev, contexts, incremental_state)`, decoder_flattened.py:96-146 driven by
+// `_generate`, transformer_flattened.py:250-275): the caller owns every piece of state -- the per-layer conv input buffers
+// (dynamic.py:95-99), the position offset (positional.py:170-176) and, so that the memory projections are not redone every
+// step as the reference does, the projected K/V of the contexts.
+namespace tnt_inc {
+__global__ void set_int_kernel(int* p, int v) { *p = v; }
+}  // namespace tnt_inc
+
+extern "C" size_t tnt_decoder_kv_cache_bytes(const tnt_decoder* d, int B, int S) {
+  if (!d || B < 0 || S < 0) return 0;
+  return static_cast<size_t>(S + 2) * B * d->cfg.n_layers * 2 * d->cfg.d * d->esz();
+}
+
+extern "C" int tnt_decoder_project_kv(tnt_decoder* D, const tnt_contexts* ctx, void* const* kv_out, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized && ctx && kv_out && ctx->B > 0, "decoder_project_kv: bad arguments");
+  FwdWs w = {};
+  for (int s = 0; s < D->cfg.n_sources; ++s) {
+    TNT_CHECK_ARG(kv_out[s] && aligned16(kv_out[s]), "decoder_project_kv: K/V buffer of source %d missing / unaligned", s);
+    w.kv[s] = kv_out[s];
+  }
+  return project_kv(D, ctx, w, as_stream(stream));
+}
+
+extern "C" size_t tnt_decoder_incremental_workspace_bytes(const tnt_decoder* d, int B, int T, const int* S) {
+  if (!d || !S) return 0;
+  return carve_fwd(d, B, T, S, nullptr, false).total + 256;
+}
+
+extern "C" int tnt_decoder_forward_incremental(tnt_decoder* D, const int64_t* ids, const tnt_contexts* ctx, void* const* kv,
+                                               int start_pos, const void* const* hist_in, const int* hist_len,
+                                               void* const* hist_out, void* X_out, float* attn_out, void* workspace,
+                                               size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized, "decoder_forward_incremental: decoder not finalized");
+  TNT_CHECK_ARG(ids && ctx && kv && X_out && workspace && hist_len, "decoder_forward_incremental: null pointer");
+  const int B = ctx->B, T = ctx->T, Ls = D->cfg.n_layers;
+  TNT_CHECK_ARG(B > 0 && T > 0 && start_pos >= 0, "decoder_forward_incremental: empty batch");
+  TNT_CHECK_ARG(start_pos + T + D->cfg.pad_idx + 1 <= D->cfg.max_positions,
+                "decoder_forward_incremental: position %d exceeds the position table", start_pos + T);
+  TNT_CHECK_ALIGN((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "decoder_forward_incremental: workspace alignment");
+  FwdWs w = carve_fwd(D, B, T, ctx->S, workspace, false);
+  if (w.total + 256 > workspace_bytes) {
+    set_error("decoder_forward_incremental: workspace %zu < %zu", workspace_bytes, w.total + 256);
+    return TNT_ERR_WORKSPACE;
+  }
+  for (int s = 0; s < D->cfg.n_sources; ++s) {
+    TNT_CHECK_ARG(kv[s], "decoder_forward_incremental: K/V cache of source %d missing (tnt_decoder_project_kv)", s);
+    w.kv[s] = const_cast<void*>(kv[s]);
+  }
+  cudaStream_t st = as_stream(stream);
+  int* pos_dev = reinterpret_cast<int*>(static_cast<char*>(workspace) + w.total);
+  tnt_inc::set_int_kernel<<<1, 1, 0, st>>>(pos_dev, start_pos);
+  TNT_LAUNCHED();
+  TNT_TRY(embed(D, ids, B, T, w.X0, pos_dev, st));
+  void* cur = w.X0;
+  for (int l = 0; l < Ls; ++l) {
+    const bool last = l == Ls - 1;
+    void* out = last ? X_out : w.X0;
+    ConvHist ch = {hist_in ? hist_in[l] : nullptr, hist_len[l], hist_out ? hist_out[l] : nullptr};
+    TNT_TRY(run_layer(D, l, ctx, w, cur, out, B, T, nullptr, nullptr, last ? attn_out : nullptr, last, st, 1, nullptr, &ch));
     cur = out;
   }
   return TNT_OK;

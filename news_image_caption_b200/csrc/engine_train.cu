@@ -459,34 +459,37 @@ extern "C" int tnt_decoder_set_grad(tnt_decoder* d, const char* key, float* grad
   return TNT_OK;
 }
 
-extern "C" int tnt_decoder_train_step(tnt_decoder* D, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,
-                                      float loss_scale, float* out2, void* workspace, size_t workspace_bytes,
-                                      tnt_stream stream) {
-  TNT_CHECK_ARG(D && D->finalized, "decoder_train_step: decoder not finalized");
-  TNT_CHECK_ARG(ids && target && ctx && out2 && workspace, "decoder_train_step: null pointer");
+namespace {
+struct StepSetup {
+  TrainWs w;
+  tnt_dropout_config drc;
+  const tnt_dropout_config* dr;
+};
+
+int step_setup(tnt_decoder* D, const tnt_contexts* ctx, void* workspace, size_t workspace_bytes, const char* who, StepSetup* s) {
   const tnt_decoder_config& cf = D->cfg;
-  const int B = ctx->B, T = ctx->T, N = B * T, d = cf.d, ns = cf.n_sources, Ls = cf.n_layers;
-  TNT_CHECK_ARG(B > 0 && T > 0, "decoder_train_step: empty batch");
-  TNT_CHECK_ARG(T + cf.pad_idx + 1 <= cf.max_positions, "decoder_train_step: T=%d exceeds the position table", T);
-  TNT_CHECK_ALIGN((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "decoder_train_step: workspace alignment");
-  TrainWs w = carve_train(D, B, T, ctx->S, workspace);
-  if (w.total > workspace_bytes) {
-    set_error("decoder_train_step: workspace %zu < %zu", workspace_bytes, w.total);
+  const int B = ctx->B, T = ctx->T, Ls = cf.n_layers;
+  TNT_CHECK_ARG(B > 0 && T > 0, "%s: empty batch", who);
+  TNT_CHECK_ARG(T + cf.pad_idx + 1 <= cf.max_positions, "%s: T=%d exceeds the position table", who, T);
+  TNT_CHECK_ALIGN((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "%s: workspace alignment", who);
+  s->w = carve_train(D, B, T, ctx->S, workspace);
+  if (s->w.total > workspace_bytes) {
+    set_error("%s: workspace %zu < %zu", who, workspace_bytes, s->w.total);
     return TNT_ERR_WORKSPACE;
   }
-  cudaStream_t st = as_stream(stream);
-  tnt_dropout_config drc = D->drop_cfg;
-  const bool drop_on = drc.dropout > 0.f || drc.input_dropout > 0.f || drc.weight_dropout > 0.f || drc.attention_dropout > 0.f ||
-                       drc.relu_dropout > 0.f;
-  drc.seed += D->drop_step++;
-  const tnt_dropout_config* dr = drop_on ? &drc : nullptr;
-  Ctx c{D, st, cf.dtype, dr};
   while (static_cast<int>(D->stage_events.size()) < Ls + 2) {
     cudaEvent_t e;
     TNT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     D->stage_events.push_back(e);
   }
-  // ---------------- forward
+  return TNT_OK;
+}
+
+// teacher-forced forward keeping every activation the backward needs; ends with X in B x T row order in w.Xbt
+int train_forward(tnt_decoder* D, const int64_t* ids, const tnt_contexts* ctx, TrainWs& w, const tnt_dropout_config* dr,
+                  cudaStream_t st) {
+  const tnt_decoder_config& cf = D->cfg;
+  const int B = ctx->B, T = ctx->T, N = B * T, d = cf.d, ns = cf.n_sources, Ls = cf.n_layers;
   {
     FwdWs f0 = layer_ws(w, 0, ns);
     TNT_TRY(project_kv(D, ctx, f0, st));
@@ -499,7 +502,15 @@ extern "C" int tnt_decoder_train_step(tnt_decoder* D, const int64_t* ids, const 
     const void* xin = l == 0 ? w.emb : w.act[l - 1].Xout;
     TNT_TRY(run_layer(D, l, ctx, f, xin, w.act[l].Xout, B, T, nullptr, nullptr, nullptr, false, st, 1, dr));
   }
-  TNT_TRY(permute_rows(w.act[Ls - 1].Xout, w.Xbt, B, T, d, cf.dtype, false, st));     // T x B -> B x T rows
+  return permute_rows(w.act[Ls - 1].Xout, w.Xbt, B, T, d, cf.dtype, false, st);     // T x B -> B x T rows
+}
+
+// AdaptiveLoss on w.Xbt, then the backward pass through loss, layers, K/V projections and embedding bands
+int train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx, float loss_scale,
+                   float* out2, TrainWs& w, const tnt_dropout_config* dr, cudaStream_t st) {
+  const tnt_decoder_config& cf = D->cfg;
+  const int B = ctx->B, T = ctx->T, N = B * T, d = cf.d, ns = cf.n_sources, Ls = cf.n_layers;
+  Ctx c{D, st, cf.dtype, dr};
   TNT_TRY(adasoftmax_nll(D->ada, w.Xbt, d, target, N, cf.pad_idx, out2, w.loss_fwd, w.loss_fwd_bytes, st));
   // ---------------- backward: loss
   const int nt = cf.n_clusters - 1;
@@ -524,10 +535,63 @@ extern "C" int tnt_decoder_train_step(tnt_decoder* D, const int64_t* ids, const 
     for (int s = 0; s < ns; ++s) TNT_TRY(kv_param_grads(c, ctx, w, l, s));
     TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], st));
   }
+  const tnt_dropout d_emb = drop_site(dr, dr ? dr->dropout : 0.f, TNT_DROP_SITE_EMBED);
   if (d_emb.p > 0.f) TNT_TRY(dropout_apply(w.gA, d, nullptr, 0, w.gA, d, N, d, cf.dtype, d_emb, st));
   TNT_TRY(embed_bwd(c, ids, B, T, w, w.gA));
   TNT_CUDA(cudaEventRecord(D->stage_events[Ls + 1], st));
   return TNT_OK;
+}
+
+// the dropout configuration of the step being issued: step k after tnt_decoder_set_dropout draws its masks with seed + k
+const tnt_dropout_config* next_dropout(tnt_decoder* D, tnt_dropout_config* drc) {
+  *drc = D->drop_cfg;
+  const bool on = drc->dropout > 0.f || drc->input_dropout > 0.f || drc->weight_dropout > 0.f || drc->attention_dropout > 0.f ||
+                  drc->relu_dropout > 0.f;
+  drc->seed += D->drop_step++;
+  return on ? drc : nullptr;
+}
+}  // namespace
+
+extern "C" int tnt_decoder_train_step(tnt_decoder* D, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,
+                                      float loss_scale, float* out2, void* workspace, size_t workspace_bytes,
+                                      tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized, "decoder_train_step: decoder not finalized");
+  TNT_CHECK_ARG(ids && target && ctx && out2 && workspace, "decoder_train_step: null pointer");
+  StepSetup s;
+  TNT_TRY(step_setup(D, ctx, workspace, workspace_bytes, "decoder_train_step", &s));
+  s.dr = next_dropout(D, &s.drc);
+  cudaStream_t st = as_stream(stream);
+  TNT_TRY(train_forward(D, ids, ctx, s.w, s.dr, st));
+  return train_backward(D, ids, target, ctx, loss_scale, out2, s.w, s.dr, st);
+}
+
+// The same step in two calls, for callers whose forward and loss are separate module calls (the reference model computes
+// `decoder(...)`, then `criterion(...)`, then `loss.backward()`: transformer_faces_objects.py:79-88,
+// callback_apex_trainer.py:229-233).  train_forward keeps the activations in `workspace`; train_backward must be given
+// the SAME ids / contexts / workspace, untouched in between.
+extern "C" int tnt_decoder_train_forward(tnt_decoder* D, const int64_t* ids, const tnt_contexts* ctx, void* X_out, void* workspace,
+                                         size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized, "decoder_train_forward: decoder not finalized");
+  TNT_CHECK_ARG(ids && ctx && X_out && workspace, "decoder_train_forward: null pointer");
+  StepSetup s;
+  TNT_TRY(step_setup(D, ctx, workspace, workspace_bytes, "decoder_train_forward", &s));
+  D->pending_dr_on = next_dropout(D, &D->pending_drc) != nullptr;
+  D->pending_ws = workspace;
+  cudaStream_t st = as_stream(stream);
+  TNT_TRY(train_forward(D, ids, ctx, s.w, D->pending_dr_on ? &D->pending_drc : nullptr, st));
+  TNT_CUDA(cudaMemcpyAsync(X_out, s.w.Xbt, static_cast<size_t>(ctx->B) * ctx->T * D->cfg.d * D->esz(), cudaMemcpyDeviceToDevice, st));
+  return TNT_OK;
+}
+
+extern "C" int tnt_decoder_train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,
+                                          float loss_scale, float* out2, void* workspace, size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized, "decoder_train_backward: decoder not finalized");
+  TNT_CHECK_ARG(ids && target && ctx && out2 && workspace, "decoder_train_backward: null pointer");
+  TNT_CHECK_ARG(D->pending_ws == workspace, "decoder_train_backward: no matching tnt_decoder_train_forward on this workspace");
+  StepSetup s;
+  TNT_TRY(step_setup(D, ctx, workspace, workspace_bytes, "decoder_train_backward", &s));
+  D->pending_ws = nullptr;
+  return train_backward(D, ids, target, ctx, loss_scale, out2, s.w, D->pending_dr_on ? &D->pending_drc : nullptr, as_stream(stream));
 }
 
 extern "C" int tnt_decoder_train_stages(const tnt_decoder* d) { return d ? d->cfg.n_layers + 2 : 0; }

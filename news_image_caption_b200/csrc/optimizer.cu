@@ -98,3 +98,69 @@ extern "C" int tnt_bert_adam_step(const tnt_adam_params* a, tnt_stream stream) {
   TNT_LAUNCHED();
   return TNT_OK;
 }
+
+// ------------------------------------------------------------------------------ torch.optim.Adam + accumulate
+namespace tnt {
+namespace {
+// torch.optim.Adam (the final* scripts: Adam(lr, betas=(0.9, 0.98), eps=1e-9) under the Noam schedule,
+// final_roberta2/custom_v4.py:421-430, 491-498): g' = g + wd p; m, v moments; bias-corrected step
+//   p -= lr / (1 - b1^t) * m / (sqrt(v) / sqrt(1 - b2^t) + eps)
+__global__ void __launch_bounds__(256) adam_kernel(float* p, const float* g, float* m, float* v, long n4, const float* gscale_dev,
+                                                   float gscale, float lr, float b1, float b2, float eps, float wd, float c1, float c2) {
+  const float coef = gscale * (gscale_dev ? *gscale_dev : 1.f);
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < n4; i += gridDim.x * 256L) {
+    const float4 gg = reinterpret_cast<const float4*>(g)[i];
+    float4 pp = reinterpret_cast<float4*>(p)[i], mm = reinterpret_cast<float4*>(m)[i], vv = reinterpret_cast<float4*>(v)[i];
+    float* pa = &pp.x; float* ma = &mm.x; float* va = &vv.x;
+    const float* ga = &gg.x;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float gr = ga[j] * coef + wd * pa[j];
+      ma[j] = b1 * ma[j] + (1.f - b1) * gr;
+      va[j] = b2 * va[j] + (1.f - b2) * gr * gr;
+      pa[j] -= (lr / c1) * ma[j] / (sqrtf(va[j]) / c2 + eps);
+    }
+    reinterpret_cast<float4*>(p)[i] = pp;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    reinterpret_cast<float4*>(v)[i] = vv;
+  }
+}
+// dst += alpha * (*alpha_dev) * src: autograd's ".grad += upstream * local gradient" for the fused engine backward
+__global__ void __launch_bounds__(256) axpy_kernel(float* dst, const float* src, long n4, float alpha, const float* alpha_dev) {
+  const float a = alpha * (alpha_dev ? *alpha_dev : 1.f);
+  for (long i = blockIdx.x * 256L + threadIdx.x; i < n4; i += gridDim.x * 256L) {
+    const float4 s = reinterpret_cast<const float4*>(src)[i];
+    float4 d = reinterpret_cast<float4*>(dst)[i];
+    d.x = fmaf(a, s.x, d.x); d.y = fmaf(a, s.y, d.y); d.z = fmaf(a, s.z, d.z); d.w = fmaf(a, s.w, d.w);
+    reinterpret_cast<float4*>(dst)[i] = d;
+  }
+}
+}  // namespace
+}  // namespace tnt
+
+extern "C" int tnt_adam_step(float* params, const float* grads, float* m, float* v, int64_t n, const float* grad_scale_dev,
+                             float grad_scale, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                             tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(params && grads && m && v && n >= 0 && n % 4 == 0 && step >= 1, "adam: bad arguments (n %% 4 == 0, step >= 1)");
+  TNT_CHECK_ALIGN(aligned16(params) && aligned16(grads) && aligned16(m) && aligned16(v), "adam: alignment");
+  if (n == 0) return TNT_OK;
+  const float c1 = 1.f - powf(beta1, static_cast<float>(step));
+  const float c2 = sqrtf(1.f - powf(beta2, static_cast<float>(step)));
+  const int grid = static_cast<int>(std::min<long>((n / 4 + 255) / 256, 16L * num_sms()));
+  adam_kernel<<<grid, 256, 0, as_stream(stream)>>>(params, grads, m, v, n / 4, grad_scale_dev, grad_scale != 0.f ? grad_scale : 1.f, lr,
+                                                   beta1, beta2, eps, weight_decay, c1, c2);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+extern "C" int tnt_grad_accumulate(float* dst, const float* src, int64_t n, float alpha, const float* alpha_dev, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(dst && src && n >= 0 && n % 4 == 0, "grad_accumulate: bad arguments (n %% 4 == 0)");
+  TNT_CHECK_ALIGN(aligned16(dst) && aligned16(src), "grad_accumulate: alignment");
+  if (n == 0) return TNT_OK;
+  const int grid = static_cast<int>(std::min<long>((n / 4 + 255) / 256, 16L * num_sms()));
+  axpy_kernel<<<grid, 256, 0, as_stream(stream)>>>(dst, src, n / 4, alpha, alpha_dev);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}

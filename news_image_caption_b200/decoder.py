@@ -13,6 +13,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
+from . import state as S_
 from ._lib import TNT_BF16, TNT_F32
 
 # concat order: decoder_faces_objects.py:296-383 (image, article, faces, obj), decoder_entity_pointer.py:287-340 (image, article, entity)
@@ -125,6 +126,14 @@ class DynamicConvDecoder(nn.Module):
         self._weights = None
         self._dirty = True
         self._ws = {}
+        self._pending = None
+        # incremental_state keys, reference scheme (utils/state.py:17-26): one DynamicConv1dTBC input buffer per layer, the
+        # positional embedder's step counter, and (this mirror's own) the projected K/V of the contexts
+        self._conv_keys = [S_.full_key('DynamicConv1dTBC', S_.new_instance_id('DynamicConv1dTBC'), 'input_buffer')
+                           for _ in self.kernels]
+        self._pos_key = S_.full_key('SinusoidalPositionalEmbedding', S_.new_instance_id('SinusoidalPositionalEmbedding'),
+                                    'position')
+        self._kv_key = S_.full_key(type(self).__name__, S_.new_instance_id(type(self).__name__), 'projected_kv')
         self.register_load_state_dict_post_hook(lambda m, ik: setattr(m, '_dirty', True))
 
     # ------------------------------------------------------------------ state_dict compatibility
@@ -184,9 +193,15 @@ class DynamicConvDecoder(nn.Module):
         _lib.check(L.tnt_decoder_finalize(self._handle, _stream()), 'tnt_decoder_finalize')
         torch.cuda.current_stream().synchronize()     # `keep` may be released after this
         self._dirty = False
+        self._seen_version = self._param_version()
+
+    def _param_version(self):
+        """Sum of the parameters' in-place version counters: any torch optimizer / in-place edit of a parameter bumps it, so
+        the prepared (folded, cast, fused) weights are rebuilt before the next engine call without the caller saying so."""
+        return sum(p._version for p in self.parameters())
 
     def _h(self):
-        if self._dirty or self._handle is None:
+        if self._dirty or self._handle is None or self._param_version() != getattr(self, '_seen_version', -1):
             self.prepare()
         return self._handle
 
@@ -241,12 +256,15 @@ class DynamicConvDecoder(nn.Module):
     def forward(self, prev_target, contexts, incremental_state=None, need_attn=True):
         """ids [B,T] (or {'roberta': ids}) -> (X [B,T,d], {'attn': [B,T,S_article+2] | None}; the entity attention when
         the decoder has an 'entity' source, decoder_entity_pointer.py:326-334) --
-        decoder_flattened.py:96-146.  `incremental_state` selects single-step decoding and is handled
-        by `generate()`; passing one here raises (the engine owns the incremental buffers)."""
-        if incremental_state is not None:
-            raise NotImplementedError('step-wise decoding is driven by DynamicConvDecoder.generate()')
+        decoder_flattened.py:96-146.  With an `incremental_state` dict the call is one step of the reference's step-wise
+        protocol (`_generate`, transformer_flattened.py:250-275): ids are the NEW tokens only and the state in the dict is
+        advanced (see `_forward_incremental`).  `generate()` is the fast device-resident loop; this is the drop-in one."""
         ids = prev_target['roberta'] if isinstance(prev_target, dict) else prev_target
         ids = ids.to('cuda', torch.long).contiguous()
+        if incremental_state is not None:
+            return self._forward_incremental(ids, contexts, incremental_state, need_attn)
+        if self.training and torch.is_grad_enabled() and getattr(self, 'flat_params', None) is not None:
+            return self._forward_autograd(ids, contexts), {'attn': None, 'inner_states': None}
         B, T = ids.shape
         L, h = _lib.lib(), self._h()
         ctx, keep = self._contexts(contexts, B, T)
@@ -260,6 +278,89 @@ class DynamicConvDecoder(nn.Module):
         _lib.check(L.tnt_decoder_forward(h, _ptr(ids), C.byref(ctx), _ptr(X), _ptr(attn), _ptr(ws), ws.numel(),
                                          _stream()), 'tnt_decoder_forward')
         return X, {'attn': attn, 'inner_states': None}
+
+    # ------------------------------------------------------------------ step-wise protocol (incremental_state)
+    def _forward_incremental(self, ids, contexts, state, need_attn=True):
+        """One call of `decoder(prev_target, contexts_i, incremental_state)`.  State kept in the caller's dict, under the
+        reference's key scheme so its filter / reorder callers keep working:
+          'DynamicConv1dTBC.<id>.input_buffer'  [<= K-1, B, d] per layer -- the conv inputs of the previous steps, oldest
+                                                first, exactly the reference's buffer (dynamic.py:95-99, 338-348);
+          'SinusoidalPositionalEmbedding.<id>.position'  tokens consumed so far (positional.py:170-176);
+          '<DecoderClass>.<id>.projected_kv'    this mirror's own: K/V of the contexts for all layers, projected ONCE (the
+                                                reference re-projects the memories in every step); re-made whenever the
+                                                batch size or the source lengths of `contexts` change."""
+        B, T = ids.shape
+        L, h = _lib.lib(), self._h()
+        ctx, keep = self._contexts(contexts, B, T)
+        S = (C.c_int * 4)(*[ctx.S[i] for i in range(4)])
+        ns, Ls = len(self.sources), len(self.kernels)
+        sig = (B, tuple(ctx.S[i] for i in range(ns)))
+        kv = state.get(self._kv_key)
+        if kv is None or kv['sig'] != sig:
+            bufs = [torch.empty(ctx.S[i] + 2, B, Ls * 2 * self.d, dtype=self.torch_dtype, device='cuda') for i in range(ns)]
+            ptrs = (C.c_void_p * 4)(*([b.data_ptr() for b in bufs] + [None] * (4 - ns)))
+            _lib.check(L.tnt_decoder_project_kv(h, C.byref(ctx), ptrs, _stream()), 'tnt_decoder_project_kv')
+            kv = {'sig': sig, 'bufs': bufs}
+            state[self._kv_key] = kv
+        start = int(state.get(self._pos_key, 0))
+        hist_in, hist_len, hist_out, new_bufs = [], [], [], []
+        for k, K in zip(self._conv_keys, self.kernels):
+            buf = state.get(k)
+            if buf is not None and buf.shape[1] != B:
+                raise ValueError('incremental_state holds conv buffers for %d rows, the batch has %d: call '
+                                 'filter_incremental_state / reorder_incremental_state first' % (buf.shape[1], B))
+            n = 0 if buf is None else buf.shape[0]
+            if buf is not None:
+                buf = buf.to(self.torch_dtype).contiguous()
+            out = torch.empty(min(K - 1, n + T), B, self.d, dtype=self.torch_dtype, device='cuda')
+            hist_in.append(buf.data_ptr() if n else None)
+            hist_len.append(n)
+            hist_out.append(out.data_ptr() if out.numel() else None)
+            new_bufs.append(out)
+            keep.append(buf)
+        ws = self._workspace('inc', L.tnt_decoder_incremental_workspace_bytes(h, B, T, S))
+        X = torch.empty(B, T, self.d, dtype=self.torch_dtype, device='cuda')
+        attn = None
+        src = 'entity' if 'entity' in self.sources else 'article'
+        if need_attn and src in self.sources:
+            attn = torch.empty(B, T, ctx.S[self.sources.index(src)] + 2, dtype=torch.float32, device='cuda')
+        kvp = (C.c_void_p * 4)(*([b.data_ptr() for b in kv['bufs']] + [None] * (4 - ns)))
+        _lib.check(L.tnt_decoder_forward_incremental(
+            h, _ptr(ids), C.byref(ctx), kvp, start, (C.c_void_p * Ls)(*hist_in), (C.c_int * Ls)(*hist_len),
+            (C.c_void_p * Ls)(*hist_out), _ptr(X), _ptr(attn), _ptr(ws), ws.numel(), _stream()), 'tnt_decoder_forward_incremental')
+        for k, out in zip(self._conv_keys, new_bufs):
+            state[k] = out
+        state[self._pos_key] = start + T
+        return X, {'attn': attn, 'inner_states': None}
+
+    def filter_incremental_state(self, incremental_state, active_idx):
+        """decoder_flattened.py:202-207: keep the rows of `active_idx` (bool [B]) in every per-row state tensor -- the conv
+        input buffers, as the reference does, and this mirror's projected K/V (skipped when every row stays)."""
+        if incremental_state is None:
+            return
+        idx = None
+        for key in list(incremental_state):
+            if 'DynamicConv1dTBC' in key:
+                incremental_state[key] = incremental_state[key][:, active_idx]
+            elif key.endswith('.projected_kv'):
+                kv = incremental_state[key]
+                if idx is None:
+                    idx = active_idx.nonzero().view(-1) if active_idx.dtype == torch.bool else active_idx
+                if idx.numel() != kv['sig'][0]:
+                    incremental_state[key] = {'sig': (idx.numel(), kv['sig'][1]),
+                                              'bufs': [b.index_select(1, idx.to(b.device)) for b in kv['bufs']]}
+
+    def reorder_incremental_state(self, incremental_state, new_order):
+        """Beam search (dynamic.py:338-348 on every layer's buffer): state rows re-gathered in `new_order`."""
+        if incremental_state is None:
+            return
+        for key in list(incremental_state):
+            if 'DynamicConv1dTBC' in key:
+                incremental_state[key] = incremental_state[key].index_select(1, new_order)
+            elif key.endswith('.projected_kv'):
+                kv = incremental_state[key]
+                incremental_state[key] = {'sig': (new_order.numel(), kv['sig'][1]),
+                                          'bufs': [b.index_select(1, new_order.to(b.device)) for b in kv['bufs']]}
 
     def nll(self, X, target):
         """AdaptiveSoftmax.forward + AdaptiveLoss(reduction='sum'): (loss_sum [1], n_non_pad) as device tensors."""
@@ -435,6 +536,7 @@ class DynamicConvDecoder(nn.Module):
         target = target.to('cuda', torch.long).contiguous()
         B, T = ids.shape
         L, h = _lib.lib(), self._h()
+        self._target_grads('grad')
         ctx, keep = self._contexts(contexts, B, T)
         S = (C.c_int * 4)(*[ctx.S[i] for i in range(4)])
         ws = self._workspace('train', L.tnt_decoder_train_workspace_bytes(h, B, T, S))
@@ -442,6 +544,72 @@ class DynamicConvDecoder(nn.Module):
         _lib.check(L.tnt_decoder_train_step(h, _ptr(ids), _ptr(target), C.byref(ctx), float(loss_scale), _ptr(out),
                                             _ptr(ws), ws.numel(), _stream()), 'tnt_decoder_train_step')
         return out
+
+    # ------------------------------------------------------------------ autograd-connected training
+    # The reference trainer does `loss.backward()` on what `model.forward` returns (callback_apex_trainer.py:229-233) after
+    # `decoder_out = self.decoder(...)`, `loss, n = self.criterion(self.decoder.adaptive_softmax, decoder_out, target)`
+    # (transformer_faces_objects.py:79-88).  After `enable_training()`, in train() mode with grad enabled, the same three
+    # calls work here: forward() runs tnt_decoder_train_forward (activations kept in the engine workspace) and returns an X
+    # that requires grad; AdaptiveLoss.forward() runs tnt_decoder_train_backward -- loss AND every parameter gradient for an
+    # upstream gradient of 1, into a staging arena -- behind a torch.autograd.Function whose backward adds
+    # upstream * staged into `.grad` (tnt_grad_accumulate), so loss scaling, gradient accumulation, zero_grad(set_to_none) and
+    # any torch optimizer over `decoder.parameters()` behave as with the reference modules.
+    def _target_grads(self, which):
+        """Point the engine's gradient outputs at `.grad` (train_step / Trainer) or at the staging arena (autograd)."""
+        if getattr(self, '_grad_target', 'grad') == which:
+            return
+        L, h = _lib.lib(), self._h()
+        if which == 'stage' and getattr(self, 'flat_stage', None) is None:
+            self.flat_stage = torch.zeros_like(self.flat_grads)
+        base = self.flat_grads if which == 'grad' else self.flat_stage
+        for k, (off, n) in self.param_slices.items():
+            _lib.check(L.tnt_decoder_set_grad(h, k.encode(), C.c_void_p(base.data_ptr() + 4 * off)), 'tnt_decoder_set_grad ' + k)
+        self._grad_target = which
+
+    def _forward_autograd(self, ids, contexts):
+        self._dirty = True                      # an optimizer may have stepped the parameters since the last call
+        L, h = _lib.lib(), self._h()
+        self._target_grads('stage')
+        B, T = ids.shape
+        ctx, keep = self._contexts(contexts, B, T)
+        S = (C.c_int * 4)(*[ctx.S[i] for i in range(4)])
+        ws = self._workspace('train', L.tnt_decoder_train_workspace_bytes(h, B, T, S))
+        X = torch.empty(B, T, self.d, dtype=self.torch_dtype, device='cuda')
+        _lib.check(L.tnt_decoder_train_forward(h, _ptr(ids), C.byref(ctx), _ptr(X), _ptr(ws), ws.numel(), _stream()),
+                   'tnt_decoder_train_forward')
+        self._pending = dict(ids=ids, ctx=ctx, keep=keep, ws=ws, X=X)
+        X.requires_grad_(True)                  # so that the loss built on it is part of the autograd graph
+        return X
+
+    def _loss_autograd(self, X, target):
+        """-> out2 [loss_sum, n_tokens]; the staging arena then holds d(loss_sum)/d(parameter)."""
+        pend = self._pending
+        if pend is None or X is not pend['X']:
+            raise RuntimeError('AdaptiveLoss: in training mode the criterion must be given the tensor decoder.forward returned '
+                               '(the fused engine backward runs from the activations of THAT forward call)')
+        L, h = _lib.lib(), self._h()
+        target = target.to('cuda', torch.long).contiguous()
+        out = torch.empty(2, dtype=torch.float32, device='cuda')
+        ws = pend['ws']
+        _lib.check(L.tnt_decoder_train_backward(h, _ptr(pend['ids']), _ptr(target), C.byref(pend['ctx']), 1.0, _ptr(out), _ptr(ws),
+                                                ws.numel(), _stream()), 'tnt_decoder_train_backward')
+        self._pending = None
+        return out
+
+    def _accumulate_staged(self, upstream):
+        """.grad += upstream * staged for every parameter (one kernel over the flat arenas)."""
+        lost = [p for _, p in self._trainable() if p.grad is None]
+        if lost:                                # optimizer.zero_grad(set_to_none=True): re-attach the arena views, zeroed
+            self.flat_grads.zero_()
+            for k, p in self._trainable():
+                off, n = self.param_slices[k]
+                p.grad = self.flat_grads[off:off + n].view(p.shape)
+        g = upstream.reshape(-1)[:1].to(torch.float32).contiguous()
+        _lib.check(_lib.lib().tnt_grad_accumulate(_ptr(self.flat_grads), _ptr(self.flat_stage), self.flat_grads.numel(), 1.0, _ptr(g),
+                                                  _stream()), 'tnt_grad_accumulate')
+
+    def _trainable(self):
+        return [(k, p) for k, p in self.named_parameters() if k in self.param_slices]
 
     def score_host(self, ids_host, target_host, contexts_host):
         """End-to-end teacher-forced scoring from PINNED HOST buffers (ids/targets int64 [B,T], contexts in
@@ -677,10 +845,34 @@ class AdaptiveLoss(nn.Module):
     def forward(self, decoder, net_output, decoder_target, reduction='sum'):
         if reduction != 'sum':
             raise NotImplementedError('reduction=%r' % reduction)
+        if getattr(decoder, '_pending', None) is not None and net_output[0].requires_grad:
+            loss, cnt = _EngineLossFn.apply(net_output[0], decoder, decoder_target)     # training: loss.backward() works
+            n = int(cnt.item())
+            decoder.check_input_errors()
+            return loss, n
         out = decoder.nll(net_output[0], decoder_target)
         n = int(out[1].item())
         decoder.check_input_errors()
         return out[:1], n
+
+
+class _EngineLossFn(torch.autograd.Function):
+    """AdaptiveSoftmax + AdaptiveLoss + the WHOLE decoder backward as one autograd node (see
+    DynamicConvDecoder._forward_autograd): forward = tnt_decoder_train_backward with an upstream gradient of 1 (loss and
+    parameter gradients in one fused pass), backward = `.grad += upstream * staged`."""
+
+    @staticmethod
+    def forward(ctx, X, decoder, target):
+        out = decoder._loss_autograd(X, target)
+        ctx.decoder = decoder
+        cnt = out[1:2].clone()
+        ctx.mark_non_differentiable(cnt)
+        return out[:1].clone(), cnt
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_cnt):
+        ctx.decoder._accumulate_staged(g_loss)
+        return None, None, None
 
 
 def sinusoid_table(n, d, padding_idx=1):

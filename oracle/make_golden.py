@@ -16,37 +16,10 @@ OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 
 
 
 def ref_greedy(dec, seed, ctx, srcs, gen_len):
-    """The reference `_generate` loop body (transformer_flattened.py:238-325) driven around the
-    REAL reference decoder object; top-1 sampling == argmax."""
-    state = {}
-    B = seed.shape[0]
-    active = seed[:, -1] != 2
-    full_active = active.clone()
-    seed_input = seed
-    lps, toks = [], [seed]
-    for i in range(gen_len):
-        prev = {'roberta': seed_input if i == 0 else seed_input[:, -1:]}
-        dec.filter_incremental_state(state, active)
-        c = {}
-        for s in srcs:
-            c[s] = ctx[s][:, full_active]
-            c[s + '_mask'] = ctx[s + '_mask'][full_active]
-        out = dec(prev, c, incremental_state=state)
-        lp = dec.get_normalized_probs((out[0][:, -1:], None), log_probs=True).squeeze(1)
-        top_lp, top_i = lp.topk(1)
-        log_prob = top_lp.new_zeros(B, 1)
-        log_prob[full_active] = top_lp
-        path = top_i.new_full((B, 1), 1)
-        path[full_active] = top_i
-        lps.append(log_prob)
-        toks.append(path)
-        seed_input = torch.cat([seed_input, top_i], -1)
-        active = top_i.squeeze(-1) != 2
-        full_active[full_active.nonzero()[~active]] = 0
-        seed_input = seed_input[active]
-        if active.sum().item() == 0:
-            break
-    return torch.cat(lps, -1), torch.cat(toks, -1)
+    """The reference `_generate` loop body (transformer_flattened.py:238-325) driven around the REAL reference decoder
+    object; top-1 sampling == argmax.  (The loop lives in oracle/restate.py so the GPU tests can drive the mirror with it.)"""
+    from .restate import module_generate_loop
+    return module_generate_loop(dec, seed, ctx, srcs, gen_len)
 
 
 def tell_case(name, nsrc, srcs, d, H, ffn, kernels, V, cut, B, T, S_img, S_art, gen_len):

@@ -522,6 +522,46 @@ def greedy_generate(seed_ids: torch.Tensor, contexts: dict, sd: SD, H: int,
     return torch.cat(lps, 1), torch.cat(toks, 1)
 
 
+def module_generate_loop(decoder, seed_ids: torch.Tensor, contexts: dict, sources=('image', 'article'),
+                         gen_len: int = 100, eos: int = 2, pad: int = 1, index: str = 'roberta'):
+    """The reference's `_generate` loop body (transformer_flattened.py:240-325 / transformer_faces_objects.py:399-494 with
+    sampling_topk = 1, where the multinomial draw over one candidate is deterministic) driven around ANY decoder object
+    that speaks the reference's module protocol: `decoder.filter_incremental_state(state, active_idx)` (:256-257),
+    `decoder(prev_target, contexts_i, incremental_state=state)` on the batch compacted to the active rows (:259-271),
+    `decoder.get_normalized_probs(...)` (:276-277), scatter of the step's ids / log-probs into [B, 1] (:303-307), EOS
+    bookkeeping (:314-323).  oracle/make_golden.py ran it around the UNMODIFIED reference decoder to freeze the
+    `greedy_ids` fixtures; tests run it around the B200 mirror.  Returns (log_probs [B, L], token_ids [B, L+1])."""
+    state: dict = {}
+    B = seed_ids.shape[0]
+    active = seed_ids[:, -1] != eos
+    full_active = active.clone()
+    seed_input = seed_ids
+    lps, toks = [], [seed_ids]
+    for i in range(gen_len):
+        prev = {index: seed_input if i == 0 else seed_input[:, -1:]}
+        decoder.filter_incremental_state(state, active)
+        c = {}
+        for s in sources:
+            c[s] = contexts[s][:, full_active]
+            c[s + '_mask'] = contexts[s + '_mask'][full_active]
+        out = decoder(prev, c, incremental_state=state)
+        lp = decoder.get_normalized_probs((out[0][:, -1:], None), log_probs=True).squeeze(1)
+        top_lp, top_i = lp.topk(1)
+        log_prob = top_lp.new_zeros(B, 1)
+        log_prob[full_active] = top_lp
+        path = top_i.new_full((B, 1), pad)
+        path[full_active] = top_i
+        lps.append(log_prob)
+        toks.append(path)
+        seed_input = torch.cat([seed_input, top_i], -1)
+        active = top_i.squeeze(-1) != eos
+        full_active[full_active.nonzero()[~active]] = 0
+        seed_input = seed_input[active]
+        if active.sum().item() == 0:
+            break
+    return torch.cat(lps, -1), torch.cat(toks, -1)
+
+
 # ----------------------------------------------------------------------------- beam search
 def beam_search(step_fn, reorder_fn, beam_size: int, seq_length: int, eos: int, return_all: bool = False):
     """`CaptionModel.beam_search` -- models/CaptionModel.py:23-122, restated for ONE caption.

@@ -378,3 +378,60 @@ def test_pointer_generation_step_attention_weights(kind):
     assert clear.sum() >= B // 2
     assert torch.equal(ids[clear, 1], best[clear])
     assert (lp[:, 0] - best_lp).abs().max().item() < 2e-2
+
+
+# ----------------------------------------------------------------------------- step-wise protocol (SURVEY 8b "Ownership")
+@pytest.mark.parametrize('name', ['tell2_small.pt', 'tell4_small.pt'])
+def test_reference_generate_loop_drives_the_mirror(name):
+    """The reference's own `_generate` loop (restated in oracle/restate.py::module_generate_loop, the function that froze
+    the greedy fixtures around the unmodified reference decoder) drives the B200 mirror through the module protocol:
+    filter_incremental_state -> decoder(prev, contexts_i, incremental_state) -> get_normalized_probs, on batches that
+    shrink as rows finish.  fp32: ids bit-exact against the reference fixture, log-probs 1e-4; the state lives in the
+    caller's dict under the reference's '{Class}.{id}.{key}' names."""
+    f = torch.load(os.path.join(G, name), weights_only=False)
+    dec = make_decoder(f['config'], f['state_dict'], torch.float32)
+    L = f['greedy_logprobs'].shape[1]
+    srcs = f['config']['sources']
+    lp, ids = O.module_generate_loop(dec, f['prev'][:, :1].cuda(), cuda_ctx(f['contexts']), srcs, gen_len=L)
+    assert torch.equal(ids.cpu(), f['greedy_ids'])
+    assert rel_err(lp, f['greedy_logprobs']) < 1e-4
+
+
+def test_incremental_state_protocol_details():
+    """Key names, buffer shapes, multi-token first call, filter / reorder semantics of the step-wise protocol against the
+    teacher-forced forward (incremental == full sequence) in fp32 and bf16."""
+    f = torch.load(os.path.join(G, 'tell2_small.pt'), weights_only=False)
+    cfg = f['config']
+    ctx = cuda_ctx(f['contexts'])
+    prev = f['prev'].cuda()
+    B, T = prev.shape
+    for dtype, tol in ((torch.float32, 1e-4), (torch.bfloat16, 3e-2)):
+        dec = make_decoder(cfg, f['state_dict'], dtype)
+        Xf, exf = dec(prev, ctx)
+        state = {}
+        X0, ex0 = dec(prev[:, :3], ctx, incremental_state=state)          # first call with 3 tokens at once
+        outs, attns = [X0], [ex0['attn']]
+        for t in range(3, T):
+            X1, ex1 = dec({'roberta': prev[:, t:t + 1]}, ctx, incremental_state=state)
+            outs.append(X1)
+            attns.append(ex1['attn'])
+        assert rel_err(torch.cat(outs, 1), Xf) < tol
+        assert rel_err(torch.cat(attns, 1), exf['attn']) < tol
+        conv = sorted(k for k in state if 'DynamicConv1dTBC' in k)
+        assert len(conv) == len(cfg['kernels']) and all(k.endswith('.input_buffer') for k in conv)
+        for k, K in zip(dec._conv_keys, cfg['kernels']):
+            assert tuple(state[k].shape) == (min(K - 1, T), B, cfg['d'])
+        assert state[dec._pos_key] == T
+        # reorder (beam search): permuted state == state of the permuted batch; filter: dropping rows == never having had them
+        order = torch.tensor([2, 0, 1] + list(range(3, B)), device='cuda')[:B]
+        st2 = {k: (v.clone() if torch.is_tensor(v) else v) for k, v in state.items()}
+        dec.reorder_incremental_state(st2, order)
+        keepm = torch.ones(B, dtype=torch.bool, device='cuda')
+        keepm[1] = False
+        dec.filter_incremental_state(st2, keepm)
+        sel = order[keepm]
+        c2 = {k: (v[:, sel] if v.dim() == 3 else v[sel]).contiguous() for k, v in ctx.items()}
+        nxt = prev[:, 1:2]
+        Xa, _ = dec(nxt[sel], c2, incremental_state=st2)
+        Xb, _ = dec(nxt, ctx, incremental_state=state)
+        assert rel_err(Xa, Xb[sel]) < tol

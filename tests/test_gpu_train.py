@@ -402,3 +402,70 @@ def test_sparse_embedding_gradient_equals_dense_scatter(dtype):
     _lib.check(L.tnt_decoder_set_sparse_embed_grad(dec._h(), None, None, None, 0), 'set_sparse off')
     dec.train_step(prev.cuda(), tgt, ctx)
     assert rel_err(dec.flat_grads, dense) < 1e-5
+
+
+@pytest.mark.parametrize('name', ['tell2_small.pt', 'tell4_small.pt'])
+def test_autograd_connected_forward_and_loss(name):
+    """the reference trainer's three calls -- decoder(...), criterion(...), loss.backward()
+    (transformer_faces_objects.py:79-88, callback_apex_trainer.py:229-233) -- work on the mirror: gradients in `.grad`
+    equal autograd through the oracle for the reference's normalised loss (sum-NLL / ln 2 / n_tokens), they ACCUMULATE over
+    two backward calls, survive optimizer.zero_grad(set_to_none=True), and a stock torch optimizer stepping
+    decoder.parameters() moves the loss exactly as it moves the oracle's."""
+    import math
+    from news_image_caption_b200 import AdaptiveLoss
+    f = torch.load(os.path.join(G, name), weights_only=False)
+    cfg = f['config']
+    dec = make_decoder(cfg, f['state_dict'], torch.float32).enable_training()
+    dec.train()
+    crit = AdaptiveLoss(1)
+    ctx = {k: v.cuda() for k, v in f['contexts'].items()}
+    prev, tgt = f['prev'].cuda(), f['target'].cuda()
+    ties = O.tied_output_keys(len(cfg['cutoffs']))
+    sd = O.leaf_state_dict(f['state_dict'], ties)
+    own = dict(dec.named_parameters())
+    trainable = {k: v for k, v in sd.items() if k in own and k not in ties and 'token_embedder_position' not in k}
+
+    def oracle_loss():
+        X, _ = O.decoder_forward(f['prev'], f['contexts'], sd, cfg['heads'], cfg['cutoffs'], cfg['sources'])
+        loss, n = O.adaptive_nll(X, f['target'], sd, cfg['cutoffs'])
+        return loss / math.log(2.0) / n, n
+
+    def mirror_loss():
+        X, _ = dec({'roberta': prev}, ctx)
+        assert X.requires_grad
+        loss, n = crit(dec, (X, None), tgt)
+        return loss / math.log(2) / n, n
+
+    lo, n_o = oracle_loss()
+    go = dict(zip(trainable, torch.autograd.grad(lo, list(trainable.values()))))
+    opt = torch.optim.SGD([p for k, p in dec.named_parameters() if k in trainable], lr=0.05)
+    opt.zero_grad(set_to_none=True)
+    lm, n = mirror_loss()
+    assert n == n_o and abs(lm.item() - lo.item()) < 1e-4 * abs(lo.item())
+    lm.backward()
+    worst = max((rel_err(own[k].grad, g), k) for k, g in go.items())
+    assert worst[0] < 2e-4, worst
+    lm2, _ = mirror_loss()                       # a second backward accumulates: .grad == 3 x the single-step gradient
+    (2 * lm2).backward()
+    worst = max((rel_err(own[k].grad, 3 * g), k) for k, g in go.items())
+    assert worst[0] < 2e-4, worst
+    # one SGD step through a stock torch optimizer on both sides, then the losses still agree
+    opt.zero_grad(set_to_none=True)
+    lm, _ = mirror_loss()
+    lm.backward()
+    opt.step()
+    with torch.no_grad():
+        for k, v in trainable.items():
+            v -= 0.05 * go[k]
+    lo2, _ = oracle_loss()
+    with torch.no_grad():
+        dec.eval()
+        X, _ = dec({'roberta': prev}, ctx)
+        l2, n2 = crit(dec, (X, None), tgt)
+        dec.train()
+    assert abs(l2.item() / math.log(2) / n2 - lo2.item()) < 1e-4 * abs(lo2.item())
+    assert lo2.item() < lo.item()                # and the step went downhill
+    # a criterion call on anything but the tensor forward() returned is refused loudly
+    X, _ = dec({'roberta': prev}, ctx)
+    with pytest.raises(RuntimeError):
+        crit(dec, (X * 1.0, None), tgt)

@@ -394,3 +394,25 @@ def test_attention_score_forward_matches_reference(separate, bias_row, zero_row)
     close(got, ref, 1e-6)
     ref_self = mh.multi_head_attention_score_forward(q, q, E, H, w, b, bias_k, zero_row, 0.0, None, None, training=False)
     close(O.mha_score(q, q, w[:E], w[E:], b[:E], b[E:], bias_k, zero_row, None, H), ref_self, 1e-6)   # qk_same branch (:92-95)
+
+
+@pytest.mark.parametrize('nsrc,srcs', [(2, ('image', 'article')), (4, ('image', 'article', 'faces', 'obj'))])
+def test_module_generate_loop_around_reference_decoder(nsrc, srcs):
+    """`O.module_generate_loop` (the reference `_generate` body, transformer_flattened.py:240-325, restated around the module
+    protocol: filter_incremental_state -> decoder(prev, contexts_i, incremental_state) -> get_normalized_probs) driven
+    around the UNMODIFIED reference decoder must reproduce the functional oracle's greedy loop -- ids exactly, log-probs
+    5e-5 -- including rows that finish early and leave the batch."""
+    torch.set_grad_enabled(False)
+    d, H, V, cut = 64, 4, 400, [100, 250]
+    dec = ri.build_ref_decoder(nsrc, d=d, heads=H, ffn=96, kernels=[3, 7], vocab=V, cutoff=list(cut)).eval()
+    sd = {k: v for k, v in dec.state_dict().items()}
+    sd['adaptive_softmax.head.class_proj.weight'] *= 0.2         # mass stays in the head: EOS (id 2) can win for some rows
+    sd['embedder.token_embedder_adaptive.embeddings.0.0.weight'][2] *= 3.0
+    dec.load_state_dict(sd, strict=False)
+    sd = dec.state_dict()
+    prev, _, ctx = synth.make_batch(6, 3, V, srcs, seed=13, S_img=5, S_art=19, S_obj=6, S_faces=3)
+    lp_m, ids_m = O.module_generate_loop(dec, prev[:, :1].clone(), ctx, srcs, gen_len=14)
+    lp_o, ids_o = O.greedy_generate(prev[:, :1], ctx, sd, H, list(cut) + [V], srcs, gen_len=14)
+    assert ids_m.shape == ids_o.shape and torch.equal(ids_m, ids_o)
+    close(lp_o, lp_m)
+    torch.set_grad_enabled(True)
