@@ -398,7 +398,9 @@ def bench_forward(env, wl, dec, sd, args, with_sustained=False):
     l_h, n_h = dec.score_host_wait((args.steps - 1) & 1)
     e2e_s = all_max(env, time.perf_counter() - t0)
     assert abs(l_h - loss_check[0].item()) < 1e-3 * abs(l_h) and int(n_h) == ntok, (l_h, loss_check, n_h, ntok)
+    h2d_full, h2d = h2d, int(env.L.tnt_decoder_last_h2d_bytes(dec._h()))     # counted by the library from the copies it issued
     res['e2e'] = {'value': ntok_all * args.steps / e2e_s, 'unit': 'tokens/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 8,
+                  'h2d_bytes_if_padding_were_copied': h2d_full,
                   'captions_per_sec': B * env.world * args.steps / e2e_s, 'ms_per_step': 1e3 * e2e_s / args.steps}
     if env.rank == 0:
         res['roofline'] = kv_roofline(B, t, ms_step)

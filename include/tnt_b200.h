@@ -573,6 +573,11 @@ int tnt_decoder_score_host(tnt_decoder* d, const int64_t* ids_host, const int64_
                            size_t staging_bytes, void* workspace, size_t workspace_bytes,
                            tnt_stream stream);
 
+/* Only the LIVE rows of a masked memory source cross PCIe: for caption b the rows s < len_b (len_b = 1 + its last un-masked
+ * position in the host mask) are one strided 2-D copy; the padded tail is never read by any kernel.  (TNT_H2D_LIVE_ROWS=0
+ * restores the full copy.)  tnt_decoder_last_h2d_bytes = bytes the last score_host / submit call actually copied. */
+uint64_t tnt_decoder_last_h2d_bytes(const tnt_decoder* d);
+
 /* Pipelined form of tnt_decoder_score_host with two slots: submit(slot) issues the H2D copies of that
  * batch on a private copy stream (overlapping the compute of the other slot), then forward + loss + the
  * D2H of (loss, n_tokens) on `stream`; wait(slot) blocks until out2_host of that slot is valid.

@@ -2,6 +2,7 @@
 // dtype) and the workspace layouts.  See engine_load.cu / engine_fwd.cu.
 #pragma once
 #include <map>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -70,6 +71,8 @@ struct tnt_decoder {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_h2d[2] = {}, ev_free[2] = {}, ev_done[2] = {};
   bool slot_used[2] = {false, false};
+  std::set<const void*> zeroed_staging;    // staging memory regions whose skipped (padded) rows have been zeroed once
+  size_t last_h2d_bytes = 0;               // host -> device bytes of the last score_host call
 
   int d() const { return cfg.d; }
   int nsrc() const { return cfg.n_sources; }

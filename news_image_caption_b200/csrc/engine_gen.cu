@@ -315,6 +315,38 @@ Staging carve_staging(const tnt_decoder* D, int B, int T, const int* S, void* ba
   s.total = off;
   return s;
 }
+
+// Host -> device copy of one memory source [S, B, E] (pinned host memory).  With a key-padding mask on the host only the
+// LIVE rows travel: caption b's rows s < len_b (len_b = 1 + its last un-masked position) are one strided 2-D copy
+// (width = one E-element row, height = len_b, pitch = B rows) -- the padded tail of an article (mean live length ~ 320 of
+// 512) is never read by any kernel (a masked key contributes exactly 0), so it need not cross PCIe.  The staging rows that
+// are skipped keep stale but FINITE values: the buffer is zeroed the first time this decoder sees it.
+int h2d_source(tnt_decoder* D, void* dst, const void* src_host, const uint8_t* mask_host, int S, int B, int E, size_t esz,
+               cudaStream_t st, size_t* bytes_out) {
+  const size_t row = static_cast<size_t>(E) * esz, all = static_cast<size_t>(S) * B * row;
+  if (!all) return TNT_OK;
+  static const bool live_only = [] { const char* e = getenv("TNT_H2D_LIVE_ROWS"); return !(e && e[0] == '0'); }();
+  if (!mask_host || !live_only) {
+    TNT_CUDA(cudaMemcpyAsync(dst, src_host, all, cudaMemcpyHostToDevice, st));
+    if (bytes_out) *bytes_out += all;
+    return TNT_OK;
+  }
+  if (!D->zeroed_staging.count(dst)) {
+    TNT_CUDA(cudaMemsetAsync(dst, 0, all, st));
+    D->zeroed_staging.insert(dst);
+  }
+  const size_t pitch = static_cast<size_t>(B) * row;
+  for (int b = 0; b < B; ++b) {
+    const uint8_t* m = mask_host + static_cast<size_t>(b) * S;
+    int len = S;
+    while (len > 0 && m[len - 1]) --len;
+    if (!len) continue;
+    TNT_CUDA(cudaMemcpy2DAsync(static_cast<char*>(dst) + b * row, pitch, static_cast<const char*>(src_host) + b * row, pitch, row, len,
+                               cudaMemcpyHostToDevice, st));
+    if (bytes_out) *bytes_out += row * len;
+  }
+  return TNT_OK;
+}
 }  // namespace
 }  // namespace tnt
 
@@ -340,13 +372,14 @@ extern "C" int tnt_decoder_score_host(tnt_decoder* D, const int64_t* ids_host, c
   cudaStream_t st = as_stream(stream);
   TNT_CUDA(cudaMemcpyAsync(s.ids, ids_host, sizeof(int64_t) * B * T, cudaMemcpyHostToDevice, st));
   TNT_CUDA(cudaMemcpyAsync(s.tgt, target_host, sizeof(int64_t) * B * T, cudaMemcpyHostToDevice, st));
+  D->last_h2d_bytes = 2 * sizeof(int64_t) * B * T;
   tnt_contexts cd = *ch;
   for (int i = 0; i < D->cfg.n_sources; ++i) {
-    const size_t mb = static_cast<size_t>(ch->S[i]) * B * D->cfg.source_dim[i] * D->esz();
-    if (mb) TNT_CUDA(cudaMemcpyAsync(s.mem[i], ch->memory[i], mb, cudaMemcpyHostToDevice, st));
+    TNT_TRY(h2d_source(D, s.mem[i], ch->memory[i], ch->pad_mask[i], ch->S[i], B, D->cfg.source_dim[i], D->esz(), st, &D->last_h2d_bytes));
     cd.memory[i] = s.mem[i];
     if (ch->pad_mask[i] && ch->S[i]) {
       TNT_CUDA(cudaMemcpyAsync(s.mask[i], ch->pad_mask[i], static_cast<size_t>(ch->S[i]) * B, cudaMemcpyHostToDevice, st));
+      D->last_h2d_bytes += static_cast<size_t>(ch->S[i]) * B;
       cd.pad_mask[i] = s.mask[i];
     } else {
       cd.pad_mask[i] = nullptr;
@@ -391,13 +424,14 @@ extern "C" int tnt_decoder_score_host_submit(tnt_decoder* D, int slot, const int
   if (D->slot_used[slot]) TNT_CUDA(cudaStreamWaitEvent(cs, D->ev_free[slot], 0));   // staging of this slot consumed
   TNT_CUDA(cudaMemcpyAsync(s.ids, ids_host, sizeof(int64_t) * B * T, cudaMemcpyHostToDevice, cs));
   TNT_CUDA(cudaMemcpyAsync(s.tgt, target_host, sizeof(int64_t) * B * T, cudaMemcpyHostToDevice, cs));
+  D->last_h2d_bytes = 2 * sizeof(int64_t) * B * T;
   tnt_contexts cd = *ch;
   for (int i = 0; i < D->cfg.n_sources; ++i) {
-    const size_t mb = static_cast<size_t>(ch->S[i]) * B * D->cfg.source_dim[i] * D->esz();
-    if (mb) TNT_CUDA(cudaMemcpyAsync(s.mem[i], ch->memory[i], mb, cudaMemcpyHostToDevice, cs));
+    TNT_TRY(h2d_source(D, s.mem[i], ch->memory[i], ch->pad_mask[i], ch->S[i], B, D->cfg.source_dim[i], D->esz(), cs, &D->last_h2d_bytes));
     cd.memory[i] = s.mem[i];
     if (ch->pad_mask[i] && ch->S[i]) {
       TNT_CUDA(cudaMemcpyAsync(s.mask[i], ch->pad_mask[i], static_cast<size_t>(ch->S[i]) * B, cudaMemcpyHostToDevice, cs));
+      D->last_h2d_bytes += static_cast<size_t>(ch->S[i]) * B;
       cd.pad_mask[i] = s.mask[i];
     } else {
       cd.pad_mask[i] = nullptr;
@@ -419,6 +453,10 @@ extern "C" int tnt_decoder_score_host_submit(tnt_decoder* D, int slot, const int
   D->slot_used[slot] = true;
   return TNT_OK;
 }
+
+// host -> device bytes the last tnt_decoder_score_host / _submit call copied (ids, targets, masks and the LIVE rows of every
+// memory source): what bench.py reports as e2e.h2d_bytes_per_step
+extern "C" uint64_t tnt_decoder_last_h2d_bytes(const tnt_decoder* D) { return D ? D->last_h2d_bytes : 0; }
 
 extern "C" int tnt_decoder_score_host_wait(tnt_decoder* D, int slot) {
   TNT_CHECK_ARG(D && (slot == 0 || slot == 1) && D->slot_used[slot], "score_host_wait: slot was not submitted");
