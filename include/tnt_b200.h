@@ -306,6 +306,9 @@ typedef struct {
   const void* dout;
   void* dq; void* dk; void* dv;
   void* scratch; size_t scratch_bytes;   /* tnt_xattn_bwd_scratch_bytes(B, T, H, D) */
+  const float* dweights;                 /* optional [B, T, S] fp32: gradient w.r.t. the head-averaged `weights` the forward
+                                            returned (multi_head.py:478-482) -- the copy heads of the pointer decoders
+                                            differentiate through them; selects the SIMT kernel */
 } tnt_xattn_bwd_params;
 size_t tnt_xattn_bwd_scratch_bytes(int B, int T, int H, int D);
 int tnt_xattn_bwd(const tnt_xattn_bwd_params* p, tnt_stream stream);
@@ -517,6 +520,24 @@ int tnt_decoder_train_forward(tnt_decoder* d, const int64_t* ids, const tnt_cont
                               size_t workspace_bytes, tnt_stream stream);
 int tnt_decoder_train_backward(tnt_decoder* d, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,
                                float loss_scale, float* out2, void* workspace, size_t workspace_bytes, tnt_stream stream);
+
+/* Training through a head that sits ON TOP of the decoder -- the copy heads of DynamicConvDecoderPointer and
+ * DynamicConvDecoderEntityPointer (decoder_pointer.py:138-216, transformer_entity_pointer.py:123-131, 185-261; ttl/run.sh
+ * trains h2_entity_pointer).  The heavy parts stay in the engine, the p_gen / mix arithmetic on [rows] and [rows, S]
+ * tensors is left to the host's autograd:
+ *   train_forward_ext   = train_forward + attn_out [B, T, S_w + 2] fp32 (last layer, head-averaged, copied source) and
+ *                         emb_out [B, T, d] (`inp_embed`: the embedder output before dropout);
+ *   target_logprob      lp[r] = log softmax_full(x_r)[target_r] (0 for pad targets): AdaptiveSoftmax.get_log_prob gathered
+ *                       at the target without writing the [rows, V] matrix;
+ *   train_backward_ext  upstream gradients row_w[r] = dL/d lp_r, dX [B, T, d] (may be NULL), dattn [B, T, S_w + 2] fp32
+ *                       (may be NULL), demb [B, T, d] (may be NULL) -> every parameter gradient, as train_backward. */
+int tnt_decoder_train_forward_ext(tnt_decoder* d, const int64_t* ids, const tnt_contexts* ctx, void* X_out, float* attn_out,
+                                  void* emb_out, void* workspace, size_t workspace_bytes, tnt_stream stream);
+int tnt_decoder_target_logprob(tnt_decoder* d, const int64_t* target, const tnt_contexts* ctx, float* lp_out, void* workspace,
+                               size_t workspace_bytes, tnt_stream stream);
+int tnt_decoder_train_backward_ext(tnt_decoder* d, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,
+                                   const float* row_w, const void* dX, const float* dattn, const void* demb, void* workspace,
+                                   size_t workspace_bytes, tnt_stream stream);
 
 /* Overlapping the gradient exchange with the backward pass: the step completes its gradients in stages --
  * stage 0: softmax-only parameters (class_proj, tail projections); stage 1+i: every parameter of layer

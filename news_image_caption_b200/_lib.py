@@ -112,7 +112,7 @@ class XattnParams(C.Structure):
 
 class XattnBwdParams(C.Structure):
     _fields_ = [('fwd', XattnParams), ('dout', vp), ('dq', vp), ('dk', vp), ('dv', vp), ('scratch', vp),
-                ('scratch_bytes', C.c_size_t)]
+                ('scratch_bytes', C.c_size_t), ('dweights', vp)]
 
 
 class AdamParams(C.Structure):
@@ -208,6 +208,9 @@ _SIGS = {
     'tnt_decoder_train_step': (i32, [vp, vp, vp, C.POINTER(Contexts), f32, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_train_forward': (i32, [vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp]),
     'tnt_decoder_train_backward': (i32, [vp, vp, vp, C.POINTER(Contexts), f32, vp, vp, C.c_size_t, vp]),
+    'tnt_decoder_train_forward_ext': (i32, [vp, vp, C.POINTER(Contexts), vp, vp, vp, vp, C.c_size_t, vp]),
+    'tnt_decoder_target_logprob': (i32, [vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp]),
+    'tnt_decoder_train_backward_ext': (i32, [vp, vp, vp, C.POINTER(Contexts), vp, vp, vp, vp, vp, C.c_size_t, vp]),
     'tnt_decoder_train_stages': (i32, [vp]),
     'tnt_decoder_stream_wait_stage': (i32, [vp, i32, vp]),
     'tnt_bert_adam_step': (i32, [C.POINTER(AdamParams), vp]),

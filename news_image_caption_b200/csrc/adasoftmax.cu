@@ -136,6 +136,34 @@ __global__ void __launch_bounds__(1024) nll_reduce_kernel(const int64_t* target,
   }
 }
 
+// get_log_prob (softmax.py:193-222) gathered at the target: lp[r] = log softmax_full(x_r)[target_r] -- head term plus, for a
+// target in tail i, the tail term (NO in-cluster ignore_index here: this is F.nll_loss over the full-vocabulary
+// log-probabilities, as the pointer models compute their loss, transformer_entity_pointer.py:123-131).  pad targets -> 0.
+__global__ void __launch_bounds__(1024) target_logprob_kernel(const int64_t* target, const int* head_t, int N, AdaCuts c, int pad,
+                                                              const float4* head_stats, const float* side,
+                                                              const float4* tail_stats, const int* tail_rows, const int* counts,
+                                                              float* lp) {
+  const int nt = c.n - 1;
+  for (int r = threadIdx.x; r < N; r += 1024) {
+    float v = 0.f;
+    if (target[r] != pad) {
+      const int ht = head_t[r];
+      const float lse = head_lse(head_stats[r], side + static_cast<long>(r) * nt, nt);
+      const float zt = ht < c.cut[0] ? head_stats[r].w : side[static_cast<long>(r) * nt + ht - c.cut[0]];
+      v = zt - lse;
+    }
+    lp[r] = v;
+  }
+  __syncthreads();
+  for (int i = 0; i < nt; ++i) {
+    const int n = counts[i];
+    for (int j = threadIdx.x; j < n; j += 1024) {
+      const float4 st = tail_stats[static_cast<long>(i) * N + j];
+      lp[tail_rows[static_cast<long>(i) * N + j]] += st.w - (st.x + __logf(st.y));
+    }
+  }
+}
+
 // greedy pick: arg-max over the full vocabulary of get_log_prob (softmax.py:193-222) without building it
 __global__ void __launch_bounds__(256) greedy_pick_kernel(int N, AdaCuts c, const float4* head_stats, const float* side,
                                                           const float4* tail_stats, int64_t* tok, float* logp) {
@@ -308,6 +336,16 @@ int adasoftmax_nll(const AdaSoftmax& a, const void* x, long ldx, const int64_t* 
   return TNT_OK;
 }
 
+int adasoftmax_target_logprob(const AdaSoftmax& a, const void* x, long ldx, const int64_t* target, int N, int pad, float* lp,
+                              float* out2_scratch, void* ws, size_t ws_bytes, cudaStream_t st) {
+  TNT_TRY(adasoftmax_nll(a, x, ldx, target, N, pad, out2_scratch, ws, ws_bytes, st));     // the row statistics of every cluster
+  AdaWs w = carve(a, N, ws, false);
+  target_logprob_kernel<<<1, 1024, 0, st>>>(target, w.head_t, N, a.cuts, pad, w.head_stats, w.side, w.tail_stats, w.tail_rows,
+                                            w.counts, lp);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
 int adasoftmax_greedy(const AdaSoftmax& a, const void* x, long ldx, int N, int64_t* tok, float* logp, void* ws,
                       size_t ws_bytes, cudaStream_t st) {
   AdaWs w = carve(a, N, ws, false);
@@ -361,7 +399,7 @@ int adasoftmax_logprob(const AdaSoftmax& a, const void* x, long ldx, int N, floa
 // by re-running the logits GEMM with the EPI_SMGRAD epilogue (bf16 dZ, never fp32 logits), then
 // dX = dZ . W (NN) and dW = dZ^T . X (TN).  Tail rows are gathered / scattered through the forward's row lists.
 struct AdaBwdWs {
-  float* row_lse; int* row_tgt; void* dz; void* dact; void* dxc; float* dhead;
+  float* row_lse; int* row_tgt; void* dz; void* dact; void* dxc; float* dhead; float* row_w;
   long ldz;
   size_t total;
 };
@@ -385,6 +423,7 @@ static AdaBwdWs carve_bwd(const AdaSoftmax& a, int N, void* ws) {
   w.dact = take(E * N * a.d);
   w.dxc = take(E * N * a.d);
   w.dhead = static_cast<float*>(take(sizeof(float) * (a.cuts.cut[0] + nt) * a.d));
+  w.row_w = static_cast<float*>(take(sizeof(float) * N));
   w.total = off;
   return w;
 }
@@ -415,9 +454,13 @@ static int gemm_call(const void* A, long lda, const void* W, long ldw, void* C, 
   return launch_gemm(&lp, epi, ex, nullptr, st);
 }
 
+int gather_floats(const float* src, const int* rows, const int* count, int N, float* out, cudaStream_t st);   // backward.cu
+
 int adasoftmax_nll_bwd(const AdaSoftmax& a, const void* x, long ldx, int N, int pad, float gscale, void* ws_fwd,
                        void* dX, long lddx, float* d_head_words, float* d_class_proj, float* const* d_proj,
-                       float* const* d_out, void* ws, size_t ws_bytes, cudaStream_t st) {
+                       float* const* d_out, void* ws, size_t ws_bytes, cudaStream_t st, const float* row_w) {
+  // row_w != NULL: gradient of sum_r row_w[r] * (-lp[r]) with lp = adasoftmax_target_logprob (full log-softmax of the
+  // target: the tail term counts for every tail row) instead of the AdaptiveLoss sum with its in-cluster ignore_index
   AdaWs f = carve(a, N, ws_fwd, false);
   AdaBwdWs w = carve_bwd(a, N, ws);
   if (w.total > ws_bytes) {
@@ -432,6 +475,7 @@ int adasoftmax_nll_bwd(const AdaSoftmax& a, const void* x, long ldx, int N, int 
   // ---- head cluster
   TNT_TRY(smgrad_rows_head(f.head_stats, f.side, f.head_t, N, nt, a.cuts.cut[0], pad, w.row_lse, w.row_tgt, st));
   LseExtra ex = {w.row_tgt, nullptr, 0, nullptr, 0, w.row_lse, gscale};
+  ex.row_w = row_w;
   TNT_TRY(gemm_call(x, ldx, a.head_w, d, w.dz, w.ldz, N, nh, d, dt, dt, TNT_NT, EPI_SMGRAD, nullptr, nullptr, 0, &ex, st));
   TNT_TRY(gemm_call(w.dz, w.ldz, a.head_w, d, dX, lddx, N, d, nh, dt, dt, TNT_NN, EPI_NONE, nullptr, nullptr, 0, nullptr, st));
   TNT_TRY(gemm_call(w.dz, w.ldz, x, ldx, w.dhead, d, nh, d, N, dt, TNT_F32, TNT_TN, EPI_NONE, nullptr, nullptr, 0, nullptr, st));
@@ -446,8 +490,12 @@ int adasoftmax_nll_bwd(const AdaSoftmax& a, const void* x, long ldx, int N, int 
     const int ncols = a.cuts.cut[i + 1] - a.cuts.cut[i];
     TNT_TRY(gather_rows(x, ldx, rows, cnt, N, f.xc, d, d, dt, 0, 0, st));
     TNT_TRY(tail_proj(a, i, f.xc, d, N, cnt, f.proj, st));
-    TNT_TRY(smgrad_rows_tail(f.tail_stats + static_cast<long>(i) * N, f.tail_loc + static_cast<long>(i) * N, cnt, N, pad,
-                             w.row_lse, w.row_tgt, st));
+    TNT_TRY(smgrad_rows_tail(f.tail_stats + static_cast<long>(i) * N, f.tail_loc + static_cast<long>(i) * N, cnt, N,
+                             row_w ? -1 : pad, w.row_lse, w.row_tgt, st));
+    if (row_w) {
+      TNT_TRY(gather_floats(row_w, rows, cnt, N, w.row_w, st));
+      ex.row_w = w.row_w;
+    }
     TNT_TRY(gemm_call(f.proj, d, a.out_w[i], d, w.dz, w.ldz, N, ncols, d, dt, dt, TNT_NT, EPI_SMGRAD, cnt, nullptr, 0, &ex, st));
     TNT_TRY(gemm_call(w.dz, w.ldz, a.out_w[i], d, w.dact, d, N, d, ncols, dt, dt, TNT_NN, EPI_NONE, cnt, nullptr, 0, nullptr, st));
     TNT_TRY(gemm_call(w.dz, w.ldz, f.proj, d, d_out[i], d, ncols, d, N, dt, TNT_F32, TNT_TN, EPI_NONE, cnt, nullptr, 0, nullptr, st));

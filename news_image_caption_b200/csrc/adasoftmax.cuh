@@ -31,7 +31,11 @@ int adasoftmax_nll(const AdaSoftmax& a, const void* x, long ldx, const int64_t* 
 size_t adasoftmax_bwd_workspace_bytes(const AdaSoftmax& a, int N);
 int adasoftmax_nll_bwd(const AdaSoftmax& a, const void* x, long ldx, int N, int pad, float gscale, void* ws_fwd,
                        void* dX, long lddx, float* d_head_words, float* d_class_proj, float* const* d_proj,
-                       float* const* d_out, void* ws, size_t ws_bytes, cudaStream_t st);
+                       float* const* d_out, void* ws, size_t ws_bytes, cudaStream_t st, const float* row_w = nullptr);
+// lp[r] = log softmax over the FULL vocabulary of target[r] (0 for pad targets); leaves the row statistics in `ws` for
+// adasoftmax_nll_bwd(..., row_w): the gradient of sum_r row_w[r] * (-lp[r])
+int adasoftmax_target_logprob(const AdaSoftmax& a, const void* x, long ldx, const int64_t* target, int N, int pad, float* lp,
+                              float* out2_scratch, void* ws, size_t ws_bytes, cudaStream_t st);
 int band_rows(const int64_t* ids, int N, const int* edges, int n_bands, int* head_scratch, int* rows, int* loc,
               int* counts, cudaStream_t st);
 int adasoftmax_greedy(const AdaSoftmax& a, const void* x, long ldx, int N, int64_t* tok, float* logp, void* ws,

@@ -19,6 +19,8 @@ struct BwdArgs {
   const void* dout; void* dq; void* dk; void* dv;
   float* scratch;               // [B, H, T, D] fp32
   DropSpec drop;                // the forward's dropout on the probabilities
+  const float* dweights;        // optional [B, T, S] fp32: gradient w.r.t. the head-AVERAGED (dropped) probabilities the
+                                // forward returned as `weights` (the copy heads differentiate through them)
 };
 
 template <typename T>
@@ -126,6 +128,37 @@ __global__ void __launch_bounds__(kThreads) xattn_bwd_kernel(BwdArgs a) {
       m = mn;
     }
     if (kg == 0 && qi < nq) lse[t0 + qi] = l > 0.f ? m + __logf(l) : INFINITY;   // +inf: fully masked row -> p = 0
+    if (a.dweights) {
+      // the returned weights w[t,k] = (1/H) sum_h pd_h[t,k] add dW[t,k] / H to every head's dPd; the softmax backward's
+      // row term then gains sum_k pd[t,k] dW[t,k] / H -- one more sweep over the keys now that lse is known
+      const float Lq = l > 0.f ? m + __logf(l) : INFINITY;
+      float extra = 0.f;
+      for (int kc = 0; kc < n_kc; ++kc) {
+        __syncthreads();
+        load_tile<T>(kp, p.k_stride_s, kc * kT, min(kT, S - kc * kT), D, Ks, 1.f);
+        __syncthreads();
+        float s[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int d = 0; d < D; ++d) {
+          const float qv = Qs[qi * ld + d];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) s[e] = fmaf(qv, Ks[(kg * 4 + e) * ld + d], s[e]);
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int key = kc * kT + kg * 4 + e;
+          const float z = qi < nq ? apply_mask(p, b, t0 + qi, key, s[e]) : -INFINITY;
+          if (qi < nq && z != -INFINITY && Lq != INFINITY) {
+            float pr = __expf(z - Lq);
+            if (a.drop.thr) pr = drop_val(a.drop, ((static_cast<unsigned long long>(b) * p.H + h) * Tn + t0 + qi) * S + key, pr);
+            extra = fmaf(pr, a.dweights[(static_cast<long>(b) * Tn + t0 + qi) * S + key], extra);
+          }
+        }
+      }
+#pragma unroll
+      for (int o = 1; o < 8; o <<= 1) extra += __shfl_xor_sync(0xffffffffu, extra, o);
+      __syncthreads();
+      if (kg == 0 && qi < nq) delta[t0 + qi] += extra / static_cast<float>(p.H);
+    }
   }
 
   // ---------------------------------------------------------------- pass B
@@ -166,7 +199,9 @@ __global__ void __launch_bounds__(kThreads) xattn_bwd_kernel(BwdArgs a) {
           if (a.drop.thr)
             mk = drop_val(a.drop, ((static_cast<unsigned long long>(b) * p.H + h) * Tn + t0 + qi) * S + key0 + kk, 1.f);
           Ps[qi * 33 + kk] = pr * mk;
-          dSs[qi * 33 + kk] = pr * (mk * dp[e] - dl);
+          float dpe = dp[e];
+          if (a.dweights && qok && key0 + kk < S) dpe += a.dweights[(static_cast<long>(b) * Tn + t0 + qi) * S + key0 + kk] / static_cast<float>(p.H);
+          dSs[qi * 33 + kk] = pr * (mk * dpe - dl);
         }
       }
       __syncthreads();
@@ -253,7 +288,7 @@ int xattn_bwd(const XattnBwd* p, cudaStream_t st) {
   TNT_CHECK_ARG(p->f.n_extra == 0, "xattn_bwd: materialise the bias_k / zero rows in k, v (n_extra must be 0)");
   TNT_CHECK_ARG(p->scratch != nullptr, "xattn_bwd: fp32 scratch [B,H,T,D] missing");
   if (p->f.T == 0 || p->f.B == 0) return TNT_OK;
-  if (!g_force_simt_attn_bwd && xattn_bwd_tc_supported(p)) {
+  if (!g_force_simt_attn_bwd && !p->dweights && xattn_bwd_tc_supported(p)) {
     variant_hit(V_XATTN_BWD_TC);
     return xattn_bwd_tc(p, st);
   }
@@ -263,6 +298,7 @@ int xattn_bwd(const XattnBwd* p, cudaStream_t st) {
   a.scratch = p->scratch;
   a.f.weights = nullptr;
   a.drop = make_drop(p->f.drop);
+  a.dweights = p->dweights;
   a.dout = p->dout; a.dq = p->dq; a.dk = p->dk; a.dv = p->dv;
   const int D = p->f.D;
   const size_t smem = (4 * static_cast<size_t>(kT) * (D + 1) + 2 * kT * 33 + 2 * static_cast<size_t>(p->f.T)) * 4;
@@ -287,5 +323,6 @@ extern "C" int tnt_xattn_bwd(const tnt_xattn_bwd_params* p, tnt_stream stream) {
   b.f = p->fwd;
   b.dout = p->dout; b.dq = p->dq; b.dk = p->dk; b.dv = p->dv;
   b.scratch = static_cast<float*>(p->scratch);
+  b.dweights = p->dweights;
   return xattn_bwd(&b, as_stream(stream));
 }

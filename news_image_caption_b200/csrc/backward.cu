@@ -508,6 +508,19 @@ int pack_band_rows(const void* src, long lds, const int* loc, const int* counts,
   return TNT_OK;
 }
 
+namespace {
+__global__ void __launch_bounds__(256) gather_floats_kernel(const float* src, const int* rows, const int* count, int N, float* out) {
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j < N) out[j] = j < *count ? src[rows[j]] : 0.f;
+}
+}  // namespace
+int gather_floats(const float* src, const int* rows, const int* count, int N, float* out, cudaStream_t st) {
+  if (N == 0) return TNT_OK;
+  gather_floats_kernel<<<(N + 255) / 256, 256, 0, st>>>(src, rows, count, N, out);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
 int kv_extra_grad(const void* dkv, long ld, int S, int B, int ncols, float* out, int dtype, cudaStream_t st) {
   const int grid = (ncols + 255) / 256;
   if (dtype == TNT_BF16)

@@ -64,6 +64,7 @@ struct XattnBwd {
   const void* dout;       // [T,B,E] same strides as out
   void* dq; void* dk; void* dv;
   float* scratch;         // fp32 [B, H, T, D]
+  const float* dweights = nullptr;   // optional [B, T, S] fp32 gradient w.r.t. the forward's head-averaged `weights` (SIMT kernel)
 };
 int xattn_bwd(const XattnBwd* p, cudaStream_t st);
 

@@ -210,7 +210,8 @@ tnt_xattn_params attn_params(const tnt_decoder* D, const tnt_contexts* ctx, cons
 
 // ------------------------------------------------------------------------------ one layer, backward
 // in: gA = dL/dXout [N, d] (T x B order);  out: gA = dL/dXin
-int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xin) {
+// `dweights` (last layer only, copy heads): gradient w.r.t. the head-averaged attention weights the forward returned
+int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xin, const float* dweights = nullptr) {
   tnt_decoder* D = c.D;
   const tnt_decoder_config& cf = D->cfg;
   const LayerW& L = D->layers[l];
@@ -274,6 +275,7 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
     xb.dk = off(w.dkv[s], static_cast<size_t>(l) * 2 * d, E);
     xb.dv = off(xb.dk, d, E);
     xb.scratch = w.attn_scr;
+    xb.dweights = (dweights && s == D->article_idx) ? dweights : nullptr;
     TNT_TRY(xattn_bwd(&xb, c.st));
     // query projection parameters of this source: q_proj_weight or rows [0, d) of in_proj_weight
     float* dwq = c.grad(at + "in_proj_weight");
@@ -487,7 +489,7 @@ int step_setup(tnt_decoder* D, const tnt_contexts* ctx, void* workspace, size_t 
 
 // teacher-forced forward keeping every activation the backward needs; ends with X in B x T row order in w.Xbt
 int train_forward(tnt_decoder* D, const int64_t* ids, const tnt_contexts* ctx, TrainWs& w, const tnt_dropout_config* dr,
-                  cudaStream_t st) {
+                  cudaStream_t st, float* attn_out = nullptr, void* emb_out = nullptr) {
   const tnt_decoder_config& cf = D->cfg;
   const int B = ctx->B, T = ctx->T, N = B * T, d = cf.d, ns = cf.n_sources, Ls = cf.n_layers;
   {
@@ -495,23 +497,31 @@ int train_forward(tnt_decoder* D, const int64_t* ids, const tnt_contexts* ctx, T
     TNT_TRY(project_kv(D, ctx, f0, st));
   }
   TNT_TRY(embed(D, ids, B, T, w.emb, nullptr, st));
+  // `inp_embed` of the pointer decoders = the embedder output BEFORE dropout, batch first (decoder_pointer.py:100-101)
+  if (emb_out) TNT_TRY(permute_rows(w.emb, emb_out, B, T, d, cf.dtype, false, st));
   const tnt_dropout d_emb = drop_site(dr, dr ? dr->dropout : 0.f, TNT_DROP_SITE_EMBED);     // decoder_flattened.py:109
   if (d_emb.p > 0.f) TNT_TRY(dropout_apply(w.emb, d, nullptr, 0, w.emb, d, N, d, cf.dtype, d_emb, st));
   for (int l = 0; l < Ls; ++l) {
     FwdWs f = layer_ws(w, l, ns);
     const void* xin = l == 0 ? w.emb : w.act[l - 1].Xout;
-    TNT_TRY(run_layer(D, l, ctx, f, xin, w.act[l].Xout, B, T, nullptr, nullptr, nullptr, false, st, 1, dr));
+    TNT_TRY(run_layer(D, l, ctx, f, xin, w.act[l].Xout, B, T, nullptr, nullptr, l == Ls - 1 ? attn_out : nullptr, false, st, 1, dr));
   }
   return permute_rows(w.act[Ls - 1].Xout, w.Xbt, B, T, d, cf.dtype, false, st);     // T x B -> B x T rows
 }
 
 // AdaptiveLoss on w.Xbt, then the backward pass through loss, layers, K/V projections and embedding bands
+// upstream gradients of a head that sits on top of the decoder (the copy heads of the pointer decoders, driven by autograd):
+// row_w[r] = dL/d lp_r with lp = adasoftmax_target_logprob (already run on w.Xbt: the statistics are in w.loss_fwd),
+// dX = dL/dX [B, T, d] beyond the softmax path, dattn = dL/d(returned attention weights) [B, T, S_w + 2],
+// demb = dL/d inp_embed [B, T, d]
+struct ExtGrads { const float* row_w; const void* dX; const float* dattn; const void* demb; };
+
 int train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx, float loss_scale,
-                   float* out2, TrainWs& w, const tnt_dropout_config* dr, cudaStream_t st) {
+                   float* out2, TrainWs& w, const tnt_dropout_config* dr, cudaStream_t st, const ExtGrads* ext = nullptr) {
   const tnt_decoder_config& cf = D->cfg;
   const int B = ctx->B, T = ctx->T, N = B * T, d = cf.d, ns = cf.n_sources, Ls = cf.n_layers;
   Ctx c{D, st, cf.dtype, dr};
-  TNT_TRY(adasoftmax_nll(D->ada, w.Xbt, d, target, N, cf.pad_idx, out2, w.loss_fwd, w.loss_fwd_bytes, st));
+  if (!ext) TNT_TRY(adasoftmax_nll(D->ada, w.Xbt, d, target, N, cf.pad_idx, out2, w.loss_fwd, w.loss_fwd_bytes, st));
   // ---------------- backward: loss
   const int nt = cf.n_clusters - 1;
   float* d_proj[TNT_MAX_CLUSTERS] = {};
@@ -524,19 +534,25 @@ int train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, co
     d_out[i] = c.grad("embedder.token_embedder_adaptive.embeddings." + std::to_string(i + 1) + ".0.weight");
     TNT_CHECK_ARG(d_proj[i] && d_out[i], "decoder_train_step: gradient buffers of softmax tail %d missing", i);
   }
-  TNT_TRY(adasoftmax_nll_bwd(D->ada, w.Xbt, d, N, cf.pad_idx, loss_scale, w.loss_fwd, w.dXbt, d, d_words, d_class, d_proj,
-                             d_out, w.loss_bwd, w.loss_bwd_bytes, st));
+  // ext: dz = row_w (onehot - p) = -row_w (p - onehot)
+  TNT_TRY(adasoftmax_nll_bwd(D->ada, w.Xbt, d, N, cf.pad_idx, ext ? -1.f : loss_scale, w.loss_fwd, w.dXbt, d, d_words, d_class,
+                             d_proj, d_out, w.loss_bwd, w.loss_bwd_bytes, st, ext ? ext->row_w : nullptr));
+  if (ext && ext->dX) TNT_TRY(add_col_blocks(w.dXbt, d, ext->dX, d, N, d, 0, 1, cf.dtype, st));
   TNT_TRY(permute_rows(w.dXbt, w.gA, B, T, d, cf.dtype, true, st));                    // B x T -> T x B rows
   // ---------------- backward: layers, K/V projections, embedding
   TNT_CUDA(cudaEventRecord(D->stage_events[0], st));
   for (int l = Ls - 1; l >= 0; --l) {
     const void* xin = l == 0 ? w.emb : w.act[l - 1].Xout;
-    TNT_TRY(layer_bwd(c, ctx, w, l, xin));
+    TNT_TRY(layer_bwd(c, ctx, w, l, xin, (ext && l == Ls - 1) ? ext->dattn : nullptr));
     for (int s = 0; s < ns; ++s) TNT_TRY(kv_param_grads(c, ctx, w, l, s));
     TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], st));
   }
   const tnt_dropout d_emb = drop_site(dr, dr ? dr->dropout : 0.f, TNT_DROP_SITE_EMBED);
   if (d_emb.p > 0.f) TNT_TRY(dropout_apply(w.gA, d, nullptr, 0, w.gA, d, N, d, cf.dtype, d_emb, st));
+  if (ext && ext->demb) {                        // inp_embed is the PRE-dropout embedder output
+    TNT_TRY(permute_rows(ext->demb, w.gB, B, T, d, cf.dtype, true, st));
+    TNT_TRY(add_col_blocks(w.gA, d, w.gB, d, N, d, 0, 1, cf.dtype, st));
+  }
   TNT_TRY(embed_bwd(c, ids, B, T, w, w.gA));
   TNT_CUDA(cudaEventRecord(D->stage_events[Ls + 1], st));
   return TNT_OK;
@@ -581,6 +597,49 @@ extern "C" int tnt_decoder_train_forward(tnt_decoder* D, const int64_t* ids, con
   TNT_TRY(train_forward(D, ids, ctx, s.w, D->pending_dr_on ? &D->pending_drc : nullptr, st));
   TNT_CUDA(cudaMemcpyAsync(X_out, s.w.Xbt, static_cast<size_t>(ctx->B) * ctx->T * D->cfg.d * D->esz(), cudaMemcpyDeviceToDevice, st));
   return TNT_OK;
+}
+
+// Variants for a head on top of the decoder (the copy heads of DynamicConvDecoderPointer / ...EntityPointer, whose small
+// p_gen / mix arithmetic the host side leaves to autograd): the forward also returns the last layer's head-averaged
+// attention over the copied source and `inp_embed`; tnt_decoder_target_logprob gives log softmax_full(x_r)[target_r] per
+// row; the backward takes the upstream gradients w.r.t. those four quantities.
+extern "C" int tnt_decoder_train_forward_ext(tnt_decoder* D, const int64_t* ids, const tnt_contexts* ctx, void* X_out, float* attn_out,
+                                             void* emb_out, void* workspace, size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized, "decoder_train_forward_ext: decoder not finalized");
+  TNT_CHECK_ARG(ids && ctx && X_out && workspace, "decoder_train_forward_ext: null pointer");
+  StepSetup s;
+  TNT_TRY(step_setup(D, ctx, workspace, workspace_bytes, "decoder_train_forward_ext", &s));
+  D->pending_dr_on = next_dropout(D, &D->pending_drc) != nullptr;
+  D->pending_ws = workspace;
+  cudaStream_t st = as_stream(stream);
+  TNT_TRY(train_forward(D, ids, ctx, s.w, D->pending_dr_on ? &D->pending_drc : nullptr, st, attn_out, emb_out));
+  TNT_CUDA(cudaMemcpyAsync(X_out, s.w.Xbt, static_cast<size_t>(ctx->B) * ctx->T * D->cfg.d * D->esz(), cudaMemcpyDeviceToDevice, st));
+  return TNT_OK;
+}
+
+extern "C" int tnt_decoder_target_logprob(tnt_decoder* D, const int64_t* target, const tnt_contexts* ctx, float* lp_out,
+                                          void* workspace, size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized && target && ctx && lp_out && workspace, "decoder_target_logprob: bad arguments");
+  TNT_CHECK_ARG(D->pending_ws == workspace, "decoder_target_logprob: no matching tnt_decoder_train_forward_ext on this workspace");
+  StepSetup s;
+  TNT_TRY(step_setup(D, ctx, workspace, workspace_bytes, "decoder_target_logprob", &s));
+  float* scratch2 = s.w.vecs;                    // the AdaptiveLoss sum of the statistics pass is not used here
+  return adasoftmax_target_logprob(D->ada, s.w.Xbt, D->cfg.d, target, ctx->B * ctx->T, D->cfg.pad_idx, lp_out, scratch2,
+                                   s.w.loss_fwd, s.w.loss_fwd_bytes, as_stream(stream));
+}
+
+extern "C" int tnt_decoder_train_backward_ext(tnt_decoder* D, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,
+                                              const float* row_w, const void* dX, const float* dattn, const void* demb,
+                                              void* workspace, size_t workspace_bytes, tnt_stream stream) {
+  TNT_CHECK_ARG(D && D->finalized, "decoder_train_backward_ext: decoder not finalized");
+  TNT_CHECK_ARG(ids && target && ctx && row_w && workspace, "decoder_train_backward_ext: null pointer");
+  TNT_CHECK_ARG(D->pending_ws == workspace, "decoder_train_backward_ext: no matching forward on this workspace");
+  TNT_CHECK_ARG(!dattn || D->article_idx >= 0, "decoder_train_backward_ext: the decoder returns no attention weights");
+  StepSetup s;
+  TNT_TRY(step_setup(D, ctx, workspace, workspace_bytes, "decoder_train_backward_ext", &s));
+  D->pending_ws = nullptr;
+  ExtGrads ext = {row_w, dX, dattn, demb};
+  return train_backward(D, ids, target, ctx, 1.f, nullptr, s.w, D->pending_dr_on ? &D->pending_drc : nullptr, as_stream(stream), &ext);
 }
 
 extern "C" int tnt_decoder_train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, const tnt_contexts* ctx,

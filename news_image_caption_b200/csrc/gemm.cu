@@ -602,6 +602,7 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
   g.alpha = p->alpha != 0.f ? p->alpha : 1.f;
   g.row_lse = lse ? lse->row_lse : nullptr;
   g.gscale = lse ? lse->gscale : 1.f;
+  g.row_w = lse ? lse->row_w : nullptr;
   static const bool pf_on = [] { const char* e = getenv("TNT_L2_PREFETCH"); return !(e && e[0] == '0'); }();
   g.pf = (pf_on && p->prefetch && aligned16(p->prefetch)) ? static_cast<const char*>(p->prefetch) : nullptr;
   g.pf_bytes = g.pf ? (p->prefetch_bytes & ~15ull) : 0;

@@ -27,6 +27,7 @@ struct GemmArgs {
   // EPI_SMGRAD: out[m, n] = gscale * (exp(z - row_lse[m]) - (n == target[m])); rows in [M_dyn, M) get zeros
   const float* row_lse;
   float gscale;
+  const float* row_w;       // optional per-row factor on top of gscale (weighted softmax gradient of the copy heads)
   // L2 prefetch hint (weights of the next GEMM of a chain), issued by the prologue
   const char* pf; unsigned long long pf_bytes;
   // dropout on the value the RESIDUAL epilogue adds the residual to / on the RELU epilogue's output (thr == 0: off)
@@ -36,6 +37,7 @@ struct GemmArgs {
 struct LseExtra {
   const int* target; float4* partials; int n_lse; float* side; long side_ld;
   const float* row_lse = nullptr; float gscale = 1.f;     // EPI_SMGRAD
+  const float* row_w = nullptr;
 };
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
@@ -90,9 +92,10 @@ __device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m
     // softmax gradient of a cluster (softmax.py:169-191 + cross_entropy backward): p - onehot(target)
     const float lse = g.row_lse[m];
     const int tgt = g.target[m];
+    const float gs = g.row_w ? g.gscale * g.row_w[m] : g.gscale;
 #pragma unroll
     for (int i = 0; i < NC; ++i)
-      acc[i] = g.gscale * (__expf(acc[i] - lse) - ((n0 + i) == tgt ? 1.f : 0.f));   // lse = +inf -> ignored row
+      acc[i] = gs * (__expf(acc[i] - lse) - ((n0 + i) == tgt ? 1.f : 0.f));   // lse = +inf -> ignored row
   }
   if (EPI == EPI_RELU_BWD) {
     const TOut* rrow = reinterpret_cast<const TOut*>(g.res) + grp * g.sres + static_cast<long>(m) * g.ldr;

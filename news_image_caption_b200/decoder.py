@@ -738,9 +738,68 @@ class DynamicConvDecoderPointer(DynamicConvDecoder):
                    'tnt_nll_rows')
         return out
 
-    def train_step(self, *a, **k):
-        raise NotImplementedError('%s: the copy head is implemented for inference / scoring / generation only'
-                                  % type(self).__name__)
+    # ------------------------------------------------------------------ training through the copy head (row f4)
+    def _p_gen_autograd(self, emb, X):
+        """p_gen [B, T] from autograd leaves emb / X [B, T, d] (fp32): sigmoid(project_p_gens(cat(inp_embed, X))),
+        decoder_pointer.py:138-141, with the weight-norm fold of GehringLinear (linear.py:30-33) in the graph."""
+        pg = self.project_p_gens
+        w = pg.weight_v * (pg.weight_g / pg.weight_v.norm(dim=1, keepdim=True))           # [1, 2d]
+        return torch.sigmoid(torch.cat((emb, X), 2) @ w.view(-1) + pg.bias)
+
+    def train_step(self, prev_target, target, contexts, copy_ids, loss_scale=1.0):
+        """Forward + the pointer models' loss F.nll_loss(log(mixed probs), target, ignore_index=pad, reduction='sum')
+        (transformer_entity_pointer.py:123-131, transformer_context_pointer.py:128) + backward.  Gradients of
+        loss_scale * loss are WRITTEN into `.grad` of every parameter (decoder, embedding bands, softmax, copy head).
+        The decoder stack, the adaptive-softmax term (log-prob of the target without the [rows, V] matrix, weighted softmax
+        gradient) and the attention backward -- incl. the gradient through the returned head-averaged weights -- run in the
+        engine (tnt_decoder_train_forward_ext / _target_logprob / _train_backward_ext); the mix arithmetic on [rows] and
+        [rows, S] tensors and the small p_gen head are chained by torch autograd.  Returns [loss_sum, n_non_pad]."""
+        if getattr(self, 'flat_params', None) is None:
+            self.enable_training()
+        ids = prev_target['roberta'] if isinstance(prev_target, dict) else prev_target
+        ids = ids.to('cuda', torch.long).contiguous()
+        target = target.to('cuda', torch.long).contiguous()
+        B, T = ids.shape
+        L, h = _lib.lib(), self._h()
+        self._target_grads('grad')
+        ctx, keep = self._contexts(contexts, B, T)
+        S = (C.c_int * 4)(*[ctx.S[i] for i in range(4)])
+        src = 'entity' if 'entity' in self.sources else 'article'
+        S_w = ctx.S[self.sources.index(src)]
+        cids = copy_ids.to('cuda', torch.long).contiguous()
+        if tuple(cids.shape) != (B, S_w):
+            raise ValueError('the copied token ids must be [B, S] of the attended source (S = %d)' % S_w)
+        ws = self._workspace('train', L.tnt_decoder_train_workspace_bytes(h, B, T, S))
+        X = torch.empty(B, T, self.d, dtype=self.torch_dtype, device='cuda')
+        emb = torch.empty(B, T, self.d, dtype=self.torch_dtype, device='cuda')
+        attn = torch.empty(B, T, S_w + 2, dtype=torch.float32, device='cuda')
+        lp = torch.empty(B, T, dtype=torch.float32, device='cuda')
+        _lib.check(L.tnt_decoder_train_forward_ext(h, _ptr(ids), C.byref(ctx), _ptr(X), _ptr(attn), _ptr(emb), _ptr(ws), ws.numel(),
+                                                   _stream()), 'tnt_decoder_train_forward_ext')
+        _lib.check(L.tnt_decoder_target_logprob(h, _ptr(target), C.byref(ctx), _ptr(lp), _ptr(ws), ws.numel(), _stream()),
+                   'tnt_decoder_target_logprob')
+        head = [p for k, p in self.named_parameters() if k.startswith(self.HOST_SIDE_KEYS)]
+        for p_ in head:
+            p_.grad.zero_()                     # autograd accumulates into the arena views; the step WRITES gradients
+        with torch.enable_grad():
+            Xl, el = X.float().requires_grad_(), emb.float().requires_grad_()
+            al, ll = attn.requires_grad_(), lp.requires_grad_()
+            p_gen = self._p_gen_autograd(el, Xl)                                            # [B, T]
+            # probability mass the copy distribution puts on the target: attention over the positions holding that token
+            # (the 2 extra keys are dropped, decoder_pointer.py:191-196)
+            hit = (cids[:, None, :] == target[:, :, None]).to(torch.float32)
+            copy_mass = (al[:, :, :S_w] * hit).sum(-1)
+            probs = p_gen * ll.exp() + (1.0 - p_gen) * copy_mass
+            logp = probs.clamp(1e-10, 1.0).log()                                            # decoder_pointer.py:213
+            nonpad = target != self.pad
+            loss = -(logp * nonpad).sum()
+            (loss * float(loss_scale)).backward()
+        dX, de = Xl.grad.to(self.torch_dtype).contiguous(), el.grad.to(self.torch_dtype).contiguous()
+        row_w = ll.grad.contiguous().view(-1)
+        dattn = al.grad.contiguous()
+        _lib.check(L.tnt_decoder_train_backward_ext(h, _ptr(ids), _ptr(target), C.byref(ctx), _ptr(row_w), _ptr(dX), _ptr(dattn),
+                                                    _ptr(de), _ptr(ws), ws.numel(), _stream()), 'tnt_decoder_train_backward_ext')
+        return torch.stack((loss.detach().float(), nonpad.sum().float()))
 
     def _head(self, copy_ids):
         """-> (tnt_pointer_head, keep-alive list) for the generation loop."""
@@ -826,6 +885,17 @@ class DynamicConvDecoderEntityPointer(DynamicConvDecoderPointer):
         lp, extra = super().forward(prev_target, contexts, entity_tokens, incremental_state, need_attn)
         extra['predictors'] = self._predictors
         return lp, extra
+
+    def _p_gen_autograd(self, emb, X):
+        """sigmoid(project_p_gens(relu(project_first_p_gens(cat(inp_embed, X))))) (transformer_entity_pointer.py:198-200): the
+        hidden layer is a tcgen05 GEMM forward and backward (modules.LinearFn), weight-norm folds stay in the graph."""
+        from .modules import linear
+        f, pg = self.project_first_p_gens, self.project_p_gens
+        w1 = f.weight_v * (f.weight_g / f.weight_v.norm(dim=1, keepdim=True))            # [hidden, 2d]
+        pred = torch.cat((emb, X), 2).to(self.torch_dtype)
+        hid = torch.relu(linear(pred, w1, f.bias).float())
+        w2 = pg.weight_v * (pg.weight_g / pg.weight_v.norm(dim=1, keepdim=True))          # [1, hidden]
+        return torch.sigmoid(hid @ w2.view(-1) + pg.bias)
 
     def _head(self, copy_ids):
         hd, keep = super()._head(copy_ids)

@@ -233,8 +233,10 @@ def xattn_tile_mask(pad_mask, S, mask_S=0):
     return out
 
 
-def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=0, lse=None, drop=None, tile_live=None):
-    """Backward of `xattn` (n_extra = 0: extra rows are ordinary k / v rows).  Returns (dq, dk, dv)."""
+def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=0, lse=None, drop=None, tile_live=None,
+              dweights=None):
+    """Backward of `xattn` (n_extra = 0: extra rows are ordinary k / v rows).  Returns (dq, dk, dv).  `dweights` [B, T, S]
+    fp32 = gradient w.r.t. the head-averaged weights the forward returned (optional)."""
     q, k, v, out, dout = [_cuda(t).contiguous() for t in (q, k, v, out, dout)]
     T, B, E = q.shape
     S = k.shape[0]
@@ -266,6 +268,9 @@ def xattn_bwd(q, k, v, out, dout, H, scale, pad_mask=None, v2_mask=None, mask_S=
     scr = torch.empty(L.tnt_xattn_bwd_scratch_bytes(B, T, H, E // H) + 256, dtype=torch.uint8, device=q.device)
     bp.dout, bp.dq, bp.dk, bp.dv = dout.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr()
     bp.scratch, bp.scratch_bytes = scr.data_ptr(), scr.numel()
+    if dweights is not None:
+        dweights = _cuda(dweights).float().contiguous()
+        bp.dweights = dweights.data_ptr()
     _lib.check(L.tnt_xattn_bwd(C.byref(bp), _st()), 'tnt_xattn_bwd')
     return dq, dk, dv
 

@@ -469,3 +469,57 @@ def test_autograd_connected_forward_and_loss(name):
     X, _ = dec({'roberta': prev}, ctx)
     with pytest.raises(RuntimeError):
         crit(dec, (X * 1.0, None), tgt)
+
+
+# ----------------------------------------------------------------------------- training through the copy heads (row f4)
+def _pointer_case(kind):
+    from news_image_caption_b200 import DynamicConvDecoderEntityPointer, DynamicConvDecoderPointer, build
+    build.build()
+    ent = kind == 'entity_pointer'
+    f = torch.load(os.path.join(G, 'entity_pointer_small.pt' if ent else 'pointer_small.pt'), weights_only=False)
+    cfg = f['config']
+    kw = dict(decoder_output_dim=cfg['d'], decoder_attention_heads=cfg['heads'], decoder_ffn_embed_dim=cfg['ffn'],
+              decoder_kernel_size_list=cfg['kernels'], vocab_size=cfg['vocab'], adaptive_softmax_cutoff=cfg['cutoffs'][:-1],
+              sources=cfg['sources'])
+    make = (lambda dt: DynamicConvDecoderEntityPointer(hidden=cfg['hidden'], dtype=dt, **kw)) if ent else \
+           (lambda dt: DynamicConvDecoderPointer(dtype=dt, **kw))
+    copy_ids = f['entity_tokens'] if ent else f['article_ids']
+    head = O.entity_pointer_forward if ent else O.pointer_decoder_forward
+    return f, cfg, make, copy_ids, head
+
+
+@pytest.mark.parametrize('kind', ['pointer', 'entity_pointer'])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_pointer_train_step_gradients(kind, dtype):
+    """ttl/run.sh trains expt/goodnews/h2_entity_pointer: loss = F.nll_loss(lprobs of the copy mix, target, ignore_index=pad,
+    sum) (transformer_entity_pointer.py:123-131; decoder_pointer.py for the plain pointer).  train_step's loss and EVERY
+    gradient -- decoder stack, embedding bands, full (not adaptive) softmax gradient, the returned attention weights'
+    path into the last layer's attention, p_gen head with its weight-norm -- against autograd through the oracle (pinned on
+    the unmodified reference classes: test_pointer_decoder_matches_reference / test_entity_pointer_decoder_matches_reference)."""
+    import torch.nn.functional as F
+    f, cfg, make, copy_ids, head = _pointer_case(kind)
+    tgt = f['target'].clone()
+    tgt[0, 2] = copy_ids[0, 1]                   # targets that ARE copy candidates: the attention path carries gradient
+    tgt[1, 4] = copy_ids[1, 0]
+    tgt[2, 1] = cfg['cutoffs'][0] + 1            # tail-local id 1: counts in the full log-softmax (no in-cluster ignore_index)
+    scale = 0.5
+    sd = O.leaf_state_dict(f['state_dict'], O.tied_output_keys(len(cfg['cutoffs'])))
+    lp_o, _, _ = head(f['prev'], f['contexts'], copy_ids, sd, cfg['heads'], cfg['cutoffs'])
+    loss_o = F.nll_loss(lp_o.view(-1, lp_o.shape[-1]), tgt.view(-1), ignore_index=1, reduction='sum')
+    (loss_o * scale).backward()
+    dec = make(dtype)
+    dec.load_reference_state_dict(f['state_dict'])
+    dec.enable_training()
+    ctx = {k: v.cuda() for k, v in f['contexts'].items()}
+    for _ in range(2):                           # twice: gradients are WRITTEN, not accumulated
+        out = dec.train_step(f['prev'].cuda(), tgt.cuda(), ctx, copy_ids.cuda(), loss_scale=scale)
+    torch.cuda.synchronize()
+    tol = 1e-4 if dtype == torch.float32 else 2e-2
+    assert int(out[1].item()) == int((tgt != 1).sum())
+    assert abs(out[0].item() - loss_o.item()) < tol * abs(loss_o.item())
+    gtol = 5e-4 if dtype == torch.float32 else 1.5e-1
+    err = rel_err if dtype == torch.float32 else l2_err
+    worst = sorted(((err(p.grad, sd[k].grad), k) for k, p in dec.named_parameters()
+                    if 'token_embedder_position' not in k and sd[k].grad is not None), reverse=True)
+    assert any('p_gens' in k for _, k in worst)
+    assert worst[0][0] < gtol, '\\n'.join('%.3e %s' % w for w in worst[:12])
