@@ -199,6 +199,7 @@ typedef struct {
   int rows, C;
   float eps;
   int dtype;
+  int variant;                    /* 0 = nn.LayerNorm; 1 = final* LayerNorm (unbiased std, eps outside), transformer_v2.py:82-94 */
 } tnt_layernorm_bwd_params;
 int tnt_layernorm_bwd(const tnt_layernorm_bwd_params* p, tnt_stream stream);
 
@@ -335,6 +336,18 @@ typedef struct {
 } tnt_lse_params;
 size_t tnt_lse_workspace_bytes(int M, int n_cols, int dtype);
 int tnt_lse_fwd(const tnt_lse_params* p, tnt_stream stream);
+
+/* Backward of Generator + CrossEntropyLoss(ignore_index = pad, reduction = 'sum') of the final* scripts
+ * (final_roberta2/transformer_v2.py:54-62, custom_v4.py:404-419, 489): from the row statistics tnt_lse_fwd wrote,
+ * dz = gscale (softmax(x W^T + b) - onehot(target)) is rebuilt by the logits GEMM's softmax-gradient epilogue (never stored in
+ * fp32), then dx [M, K] = dz W (dtype), dW [n_cols, K] = dz^T x (fp32, written), db [n_cols] = column sums (fp32, optional). */
+size_t tnt_ce_bwd_workspace_bytes(int M, int n_cols, int dtype);
+int tnt_ce_bwd(const void* x, int64_t ldx, const void* w, int64_t ldw, const float* bias, const int* target, const float* stats,
+               int M, int n_cols, int K, int pad, float gscale, void* dx, int64_t lddx, float* dW, float* db, int dtype,
+               void* workspace, size_t workspace_bytes, tnt_stream stream);
+/* nn.Embedding backward: grad[ids[r], :] += scale * dy[r, :] (fp32 atomics) -- Embeddings.lut of the final* decoder */
+int tnt_embedding_bwd(const int64_t* ids, int n, const void* dy, int64_t lddy, float scale, float* grad, int64_t ldg, int C,
+                      int vocab, int dtype, tnt_stream stream);
 
 /* ------------------------------------------------------------------------------------------
  * Decoder engine: the whole DynamicConvDecoder forward, loss, log-probs and greedy generation.

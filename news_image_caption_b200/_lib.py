@@ -82,7 +82,7 @@ class LayernormParams(C.Structure):
 
 class LayernormBwdParams(C.Structure):
     _fields_ = [('x', vp), ('ldx', i64), ('dy', vp), ('lddy', i64), ('dx', vp), ('lddx', i64), ('gamma', vp),
-                ('dgamma', vp), ('dbeta', vp), ('rows', i32), ('C', i32), ('eps', f32), ('dtype', i32)]
+                ('dgamma', vp), ('dbeta', vp), ('rows', i32), ('C', i32), ('eps', f32), ('dtype', i32), ('variant', i32)]
 
 
 class EmbedParams(C.Structure):
@@ -166,6 +166,9 @@ _SIGS = {
     'tnt_xattn_bwd': (i32, [C.POINTER(XattnBwdParams), vp]),
     'tnt_lse_workspace_bytes': (C.c_size_t, [i32, i32, i32]),
     'tnt_lse_fwd': (i32, [C.POINTER(LseParams), vp]),
+    'tnt_ce_bwd_workspace_bytes': (C.c_size_t, [i32, i32, i32]),
+    'tnt_ce_bwd': (i32, [vp, i64, vp, i64, vp, vp, vp, i32, i32, i32, i32, f32, vp, i64, vp, vp, i32, vp, C.c_size_t, vp]),
+    'tnt_embedding_bwd': (i32, [vp, i32, vp, i64, f32, vp, i64, i32, i32, i32, vp]),
     'tnt_decoder_create': (vp, [C.POINTER(DecoderConfig)]),
     'tnt_decoder_destroy': (None, [vp]),
     'tnt_decoder_weight_bytes': (C.c_size_t, [vp]),

@@ -508,6 +508,60 @@ int adasoftmax_nll_bwd(const AdaSoftmax& a, const void* x, long ldx, int N, int 
 
 }  // namespace tnt
 
+// ---------------------------------------------------------------------------- Generator + CrossEntropy backward (final*)
+namespace tnt {
+namespace {
+__global__ void __launch_bounds__(256) ce_rows_kernel(const float4* stats, const int* target, int M, int pad, float* row_lse,
+                                                      int* row_tgt) {
+  const int r = blockIdx.x * 256 + threadIdx.x;
+  if (r >= M) return;
+  const int t = target[r];
+  if (t == pad || t < 0) {                               // CrossEntropyLoss(ignore_index = pad)
+    row_lse[r] = INFINITY;
+    row_tgt[r] = -1;
+    return;
+  }
+  row_lse[r] = stats[r].x + __logf(stats[r].y);
+  row_tgt[r] = t;
+}
+}  // namespace
+}  // namespace tnt
+
+extern "C" size_t tnt_ce_bwd_workspace_bytes(int M, int n_cols, int dtype) {
+  const size_t ldz = (static_cast<size_t>(n_cols) + 7) & ~size_t(7);
+  return tnt::al256(sizeof(float) * M) + tnt::al256(sizeof(int) * M) + tnt::al256(tnt::dtype_size(dtype) * M * ldz) + 256;
+}
+
+// Backward of sum-CrossEntropy over z = x W^T + b (Generator.proj + CrossEntropyLoss(ignore_index=pad, reduction='sum'),
+// final_roberta2/transformer_v2.py:54-62, custom_v4.py:404-419, 489): dz = gscale (softmax(z) - onehot(target)) is produced
+// by re-running the logits GEMM with the softmax-gradient epilogue from the row statistics tnt_lse_fwd left in `stats`
+// (the logits are never stored in fp32); dx = dz W, dW = dz^T x (fp32), db = column sums of dz (fp32).
+extern "C" int tnt_ce_bwd(const void* x, int64_t ldx, const void* w, int64_t ldw, const float* bias, const int* target,
+                          const float* stats, int M, int n_cols, int K, int pad, float gscale, void* dx, int64_t lddx, float* dW,
+                          float* db, int dtype, void* workspace, size_t workspace_bytes, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(x && w && target && stats && dx && dW && workspace && M >= 0 && n_cols > 0 && K > 0, "ce_bwd: bad arguments");
+  TNT_CHECK_ARG(workspace_bytes >= tnt_ce_bwd_workspace_bytes(M, n_cols, dtype), "ce_bwd: workspace too small");
+  if (M == 0) return TNT_OK;
+  cudaStream_t st = as_stream(stream);
+  const long ldz = (static_cast<long>(n_cols) + 7) & ~7L;
+  char* base = static_cast<char*>(workspace);
+  float* row_lse = reinterpret_cast<float*>(base);
+  int* row_tgt = reinterpret_cast<int*>(base + al256(sizeof(float) * M));
+  void* dz = base + al256(sizeof(float) * M) + al256(sizeof(int) * M);
+  ce_rows_kernel<<<(M + 255) / 256, 256, 0, st>>>(reinterpret_cast<const float4*>(stats), target, M, pad, row_lse, row_tgt);
+  TNT_LAUNCHED();
+  LseExtra ex = {row_tgt, nullptr, 0, nullptr, 0, row_lse, gscale};
+  tnt_linear_params lp = {};
+  lp.a = x; lp.lda = ldx; lp.w = w; lp.ldw = ldw; lp.bias = bias; lp.c = dz; lp.ldc = ldz;
+  lp.M = M; lp.N = n_cols; lp.K = K; lp.groups = 1; lp.dtype_in = dtype; lp.dtype_out = dtype; lp.epilogue = EPI_NONE;
+  TNT_TRY(launch_gemm(&lp, EPI_SMGRAD, &ex, nullptr, st));
+  TNT_TRY(gemm_call(dz, ldz, w, ldw, dx, lddx, M, K, n_cols, dtype, dtype, TNT_NN, EPI_NONE, nullptr, nullptr, 0, nullptr, st));
+  TNT_TRY(gemm_call(dz, ldz, x, ldx, dW, K, n_cols, K, M, dtype, TNT_F32, TNT_TN, EPI_NONE, nullptr, nullptr, 0, nullptr, st));
+  if (db) TNT_TRY(colsum(dz, ldz, M, n_cols, nullptr, db, dtype, false, false, st));
+  return TNT_OK;
+}
+
 extern "C" size_t tnt_lse_workspace_bytes(int M, int n_cols, int dtype) {
   (void)dtype;
   return tnt::lse_partials_bytes(M, n_cols);

@@ -588,3 +588,42 @@ extern "C" int tnt_embed_grad_scatter(const void* rows, int64_t ld_rows, const i
   TNT_LAUNCHED();
   return TNT_OK;
 }
+
+// nn.Embedding backward for the final* decoder (Embeddings: lut(x) * sqrt(d_model), transformer_v2.py Embeddings):
+// grad[ids[r], :] += scale * dy[r, :] (fp32 atomics); ids outside [0, vocab) are skipped.
+namespace tnt {
+namespace {
+template <typename T>
+__global__ void __launch_bounds__(256) embedding_bwd_kernel(const int64_t* ids, int n, const T* dy, long lddy, float scale, float* grad,
+                                                            long ldg, int C, int vocab) {
+  const int lane = threadIdx.x & 31;
+  for (int r = blockIdx.x * 8 + (threadIdx.x >> 5); r < n; r += gridDim.x * 8) {
+    const long id = ids[r];
+    if (id < 0 || id >= vocab) continue;
+    const T* s = dy + static_cast<long>(r) * lddy;
+    float* d = grad + id * ldg;
+    for (int vc = lane; vc < (C >> 3); vc += 32) {
+      float v[8];
+      load8(s + vc * 8, v);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) atomicAdd(d + vc * 8 + i, v[i] * scale);
+    }
+  }
+}
+}  // namespace
+}  // namespace tnt
+
+extern "C" int tnt_embedding_bwd(const int64_t* ids, int n, const void* dy, int64_t lddy, float scale, float* grad, int64_t ldg,
+                                 int C, int vocab, int dtype, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(ids && dy && grad && n >= 0 && C % 8 == 0 && vocab > 0, "embedding_bwd: bad arguments");
+  TNT_CHECK_ALIGN(aligned16(dy) && lddy % 8 == 0, "embedding_bwd: dy alignment");
+  if (n == 0) return TNT_OK;
+  const int grid = grid_for(n, 8);
+  if (dtype == TNT_BF16)
+    embedding_bwd_kernel<bf16><<<grid, 256, 0, as_stream(stream)>>>(ids, n, static_cast<const bf16*>(dy), lddy, scale, grad, ldg, C, vocab);
+  else
+    embedding_bwd_kernel<float><<<grid, 256, 0, as_stream(stream)>>>(ids, n, static_cast<const float*>(dy), lddy, scale, grad, ldg, C, vocab);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}

@@ -120,7 +120,11 @@ __global__ void __launch_bounds__(kWarps * 32) layernorm_bwd_kernel(tnt_layernor
 #pragma unroll
       for (int j = 0; j < 8; ++j) sq = fmaf(t[j] - mean, t[j] - mean, sq);
     }
-    const float rstd = rsqrtf(warp_sum(sq) / p.C + p.eps);
+    // variant 0 (nn.LayerNorm): xhat = (x - mean) / sqrt(var_biased + eps);  variant 1 (final* LayerNorm,
+    // transformer_v2.py:82-94): xhat = (x - mean) / (std_unbiased + eps).  Both: dx = rstd (dxhat - mean(dxhat)) - xhat c2
+    const float ssq = warp_sum(sq);
+    const float sdev = sqrtf(ssq / (p.C - 1));
+    const float rstd = p.variant == 1 ? 1.f / (sdev + p.eps) : rsqrtf(ssq / p.C + p.eps);
     float s1 = 0.f, s2 = 0.f;                          // sum(dxhat), sum(dxhat * xhat)
     for (int vc = lane; vc < nv; vc += 32) {
       float t[8], d[8], g[8];
@@ -137,7 +141,8 @@ __global__ void __launch_bounds__(kWarps * 32) layernorm_bwd_kernel(tnt_layernor
       }
     }
     s1 = warp_sum(s1) / p.C;
-    s2 = warp_sum(s2) / p.C;
+    s2 = warp_sum(s2);
+    const float c2 = p.variant == 1 ? (sdev > 0.f ? s2 / ((p.C - 1) * sdev) : 0.f) : rstd * s2 / p.C;
     for (int vc = lane; vc < nv; vc += 32) {
       float t[8], d[8], g[8], o[8];
       load8(x + vc * 8, t);
@@ -146,7 +151,7 @@ __global__ void __launch_bounds__(kWarps * 32) layernorm_bwd_kernel(tnt_layernor
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float xh = (t[j] - mean) * rstd;
-        o[j] = rstd * (d[j] * g[j] - s1 - xh * s2);
+        o[j] = rstd * (d[j] * g[j] - s1) - xh * c2;
       }
       store8(dx + vc * 8, o);
     }
@@ -202,7 +207,9 @@ __global__ void __launch_bounds__(kWarps * 32) layernorm_bwd_small_kernel(tnt_la
 #pragma unroll
         for (int j = 0; j < 8; ++j) sq = fmaf(t[i][j] - mean, t[i][j] - mean, sq);
       }
-    const float rstd = rsqrtf(warp_sum(sq) * invC + p.eps);
+    const float ssq = warp_sum(sq);
+    const float sdev = sqrtf(ssq / (p.C - 1));
+    const float rstd = p.variant == 1 ? 1.f / (sdev + p.eps) : rsqrtf(ssq * invC + p.eps);
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int i = 0; i < 4; ++i)
@@ -216,14 +223,15 @@ __global__ void __launch_bounds__(kWarps * 32) layernorm_bwd_small_kernel(tnt_la
         db[i][j] += d[i][j];
       }
     s1 = warp_sum(s1) * invC;
-    s2 = warp_sum(s2) * invC;
+    s2 = warp_sum(s2);
+    const float c2 = p.variant == 1 ? (sdev > 0.f ? s2 / ((p.C - 1) * sdev) : 0.f) : rstd * s2 * invC;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int vc = lane + 32 * i;
       if (vc < nv) {
         float o[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = rstd * (d[i][j] * g[i][j] - s1 - t[i][j] * s2);
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (d[i][j] * g[i][j] - s1) - t[i][j] * c2;
         store8(dx + vc * 8, o);
       }
     }

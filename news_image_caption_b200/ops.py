@@ -165,7 +165,8 @@ def layernorm(x, gamma, beta, eps=1e-5, variant=0, transpose_tb=None):
     return y
 
 
-def layernorm_bwd(x, dy, gamma, eps=1e-5):
+def layernorm_bwd(x, dy, gamma, eps=1e-5, variant=0):
+    """Backward of `layernorm` (variant 1 = the final* LayerNorm, transformer_v2.py:82-94) -> (dx, dgamma, dbeta)."""
     x, dy = _cuda(x).contiguous(), dy.contiguous()
     Cc = x.shape[-1]
     dx = torch.empty_like(x)
@@ -175,7 +176,7 @@ def layernorm_bwd(x, dy, gamma, eps=1e-5):
     p = _lib.LayernormBwdParams()
     p.x, p.ldx, p.dy, p.lddy, p.dx, p.lddx = x.data_ptr(), Cc, dy.data_ptr(), Cc, dx.data_ptr(), Cc
     p.gamma, p.dgamma, p.dbeta = gamma.data_ptr(), dg.data_ptr(), db.data_ptr()
-    p.rows, p.C, p.eps, p.dtype = x.numel() // Cc, Cc, eps, _code(x)
+    p.rows, p.C, p.eps, p.dtype, p.variant = x.numel() // Cc, Cc, eps, _code(x), variant
     _lib.check(_lib.lib().tnt_layernorm_bwd(C.byref(p), _st()), 'tnt_layernorm_bwd')
     return dx, dg, db
 
@@ -360,3 +361,86 @@ def nan_mask(x, out_dtype=None):
     p.dtype_in, p.dtype_out = _code(x), _code(out)
     _lib.check(_lib.lib().tnt_nan_mask(C.byref(p), _st()), 'tnt_nan_mask')
     return out, mask
+
+
+def _v2_mask(p, v2_mask, B, S):
+    m = None
+    p.mask_mode = MASK_NONE
+    if v2_mask is not None:
+        m = v2_mask.to(torch.bool).expand(B, v2_mask.shape[-2], S).contiguous()
+        p.mask, p.m_stride_b, p.mask_mode = m.data_ptr(), m.shape[1] * S, MASK_V2
+        p.m_stride_t = S if m.shape[1] > 1 else 0
+    return m
+
+
+def xattn_bwd_strided(q, q_tb, k, k_sb, v, v_sb, out, dout, B, T, S, H, D, scale, v2_mask=None):
+    """Backward of `xattn_strided`: (dq, dk, dv) in the layouts (strides) of q, k, v; out / dout are [T, B, H*D]."""
+    E = H * D
+    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    out, dout = out.contiguous(), dout.contiguous()
+    bp = _lib.XattnBwdParams()
+    p = bp.fwd
+    p.q, p.q_stride_t, p.q_stride_b = q.data_ptr(), q_tb[0], q_tb[1]
+    p.k, p.k_stride_s, p.k_stride_b = k.data_ptr(), k_sb[0], k_sb[1]
+    p.v, p.v_stride_s, p.v_stride_b = v.data_ptr(), v_sb[0], v_sb[1]
+    p.out, p.o_stride_t, p.o_stride_b = out.data_ptr(), B * E, E
+    keep = _v2_mask(p, v2_mask, B, S)
+    p.B, p.T, p.S, p.H, p.D, p.n_extra, p.scale, p.dtype = B, T, S, H, D, 0, scale, _code(q)
+    L = _lib.lib()
+    scr = torch.empty(L.tnt_xattn_bwd_scratch_bytes(B, T, H, D) + 256, dtype=torch.uint8, device=q.device)
+    bp.dout, bp.dq, bp.dk, bp.dv = dout.data_ptr(), dq.data_ptr(), dk.data_ptr(), dv.data_ptr()
+    bp.scratch, bp.scratch_bytes = scr.data_ptr(), scr.numel()
+    _lib.check(L.tnt_xattn_bwd(C.byref(bp), _st()), 'tnt_xattn_bwd')
+    del keep
+    return dq, dk, dv
+
+
+def lse_stats(x, w, bias, target):
+    """`lse` returning the raw [M, 4] statistics tensor (kept for `ce_bwd`)."""
+    x, w = _cuda(x).contiguous(), w.contiguous()
+    M, K = x.shape
+    N = w.shape[0]
+    L = _lib.lib()
+    ws = torch.empty(L.tnt_lse_workspace_bytes(M, N, _code(x)) + 256, dtype=torch.uint8, device=x.device)
+    stats = torch.empty(M, 4, dtype=torch.float32, device=x.device)
+    p = _lib.LseParams()
+    p.x, p.ldx, p.w, p.ldw = x.data_ptr(), K, w.data_ptr(), K
+    p.bias = bias.data_ptr() if bias is not None else None
+    tg = target.to(torch.int32).contiguous()
+    p.target = tg.data_ptr()
+    p.stats, p.workspace, p.workspace_bytes = stats.data_ptr(), ws.data_ptr(), ws.numel()
+    p.M, p.n_cols, p.K, p.dtype = M, N, K, _code(x)
+    _lib.check(L.tnt_lse_fwd(C.byref(p), _st()), 'tnt_lse_fwd')
+    return stats
+
+
+def ce_bwd(x, w, bias, target, stats, pad, gscale):
+    """Backward of sum-CrossEntropy(x w^T + bias, target, ignore_index=pad) * gscale -> (dx [M,K] dtype, dW [N,K] fp32, db [N] fp32)."""
+    x, w = x.contiguous(), w.contiguous()
+    M, K = x.shape
+    N = w.shape[0]
+    L = _lib.lib()
+    dx = torch.empty_like(x)
+    dW = torch.empty(N, K, dtype=torch.float32, device=x.device)
+    db = torch.empty(N, dtype=torch.float32, device=x.device) if bias is not None else None
+    tg = target.to(torch.int32).contiguous()
+    ws = torch.empty(L.tnt_ce_bwd_workspace_bytes(M, N, _code(x)) + 256, dtype=torch.uint8, device=x.device)
+    _lib.check(L.tnt_ce_bwd(_p(x), K, _p(w), K, _p(bias) if bias is not None else None, _p(tg), _p(stats), M, N, K, pad, float(gscale),
+                            _p(dx), K, _p(dW), _p(db) if db is not None else None, _code(x), _p(ws), ws.numel(), _st()), 'tnt_ce_bwd')
+    return dx, dW, db
+
+
+def embedding_bwd(ids, dy, scale, vocab):
+    """grad [vocab, d] fp32 with grad[ids[r]] += scale * dy[r] (nn.Embedding backward)."""
+    ids = _cuda(ids).to(torch.long).contiguous().view(-1)
+    dy = dy.contiguous().view(ids.numel(), -1)
+    g = torch.zeros(vocab, dy.shape[1], dtype=torch.float32, device=dy.device)
+    _lib.check(_lib.lib().tnt_embedding_bwd(_p(ids), ids.numel(), _p(dy), dy.shape[1], float(scale), _p(g), dy.shape[1], dy.shape[1],
+                                            vocab, _code(dy), _st()), 'tnt_embedding_bwd')
+    return g
+
+
+def adam_step(params, grads, m, v, lr, step, betas=(0.9, 0.98), eps=1e-9, weight_decay=0.0, grad_scale=1.0):
+    """torch.optim.Adam over flat fp32 arenas (tnt_adam_step): the final* scripts' optimizer (custom_v4.py:491)."""
+    _lib.check(_lib.lib().tnt_adam_step(_p(params), _p(grads), _p(m), _p(v), params.numel(), None, float(grad_scale), float(lr),
+                                        betas[0], betas[1], eps, weight_decay, int(step), _st()), 'tnt_adam_step')

@@ -73,3 +73,68 @@ def test_v2_full_width_bf16():
     m, tv = build(cfg, sd, torch.bfloat16, 1024, 1024)
     out = m.forward({k: v.cuda() for k, v in mem.items()}, ids.cuda(), None, tv.subsequent_mask(T).cuda())
     assert rel_err(out, want) < 2e-2
+
+
+def l2_err(a, b):
+    a, b = a.float().cpu(), b.float().cpu()
+    return ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_v2_training_gradients_and_adam_noam(dtype):
+    """Rows a12-a14, training: `run_epoch` of the fork's script (custom_v4.py:287-304) -- out = model.forward(...);
+    loss, loss_node = loss_compute(out, y, ntokens); loss_node.backward(); optimizer.step(); scheduler.step() -- on the
+    mirror after enable_training().  Every gradient against autograd through the oracle (golden fixture model: pinned on
+    the unmodified reference module), then Adam(betas=(0.9, 0.98), eps=1e-9) under the Noam schedule: the fused FlatAdam
+    kernel and a stock torch.optim.Adam + LambdaLR(rate) on the oracle's leaves must move the loss identically (fp32)."""
+    f = torch.load(os.path.join(G, 'v2_small.pt'), weights_only=False)
+    cfg, sd0, mem = f['config'], f['state_dict'], f['memory']
+    m, tv = build(cfg, sd0, dtype, mem['image'].shape[-1], mem['article'].shape[-1])
+    m.enable_training()
+    memc = {k: v.cuda() for k, v in mem.items()}
+    ids, y, norm, pad = f['ids'], f['y'], float(f['ntokens']), 1
+    leaves = {k: v.clone().requires_grad_(True) for k, v in sd0.items() if v.is_floating_point() and 'pe' not in k}
+
+    def oracle_loss():
+        out = O.v2_decode(ids, mem, f['tgt_mask'], leaves, cfg['h'])
+        return O.v2_generator_loss(out, y, leaves, pad, norm)
+
+    loss_compute = tv.SimpleLossCompute(m.generator, pad)
+    own = dict(m.named_parameters())
+    opt = tv.FlatAdam(m.parameters(), lr=1.0, betas=(0.9, 0.98), eps=1e-9)
+    sched = tv.NoamScheduler(opt, cfg['d'], factor=1.0, warmup=4)
+    ref_opt = torch.optim.Adam(list(leaves.values()), lr=1.0, betas=(0.9, 0.98), eps=1e-9)
+    ref_sched = torch.optim.lr_scheduler.LambdaLR(ref_opt, lambda s: tv.rate(s, cfg['d'], 1.0, 4))
+    tol = 1e-4 if dtype == torch.float32 else 2e-2
+    losses = []
+    for step in range(3):
+        out = m.forward(memc, ids.cuda(), None, f['tgt_mask'].cuda())
+        loss, loss_node = loss_compute(out, y.cuda(), norm)
+        opt.zero_grad(set_to_none=True)
+        loss_node.backward()
+        ref_opt.zero_grad(set_to_none=True)
+        lo = oracle_loss()
+        lo.backward()
+        if dtype == torch.float32 or step == 0:
+            assert abs(loss_node.item() - lo.item()) < tol * abs(lo.item()), (step, loss_node.item(), lo.item())
+        if step == 0:                                  # every gradient, first step (identical parameters on both sides)
+            err = rel_err if dtype == torch.float32 else l2_err
+            worst = sorted(((err(own[k].grad, v.grad), k) for k, v in leaves.items()), reverse=True)
+            assert worst[0][0] < (5e-4 if dtype == torch.float32 else 1e-1), '\n'.join('%.3e %s' % w for w in worst[:10])
+        assert abs(opt.param_groups[0]['lr'] - ref_opt.param_groups[0]['lr']) < 1e-12
+        opt.step()
+        sched.step()
+        ref_opt.step()
+        ref_sched.step()
+        losses.append(loss.item())
+    if dtype == torch.float32:
+        worst = max((rel_err(own[k], v.detach()), k) for k, v in leaves.items())
+        assert worst[0] < 2e-3, worst                  # parameters after 3 Adam steps (Adam normalises ~0 gradients: loose)
+    # the fast no-grad path sees the updated parameters (cast / table caches key on the version counters)
+    with torch.no_grad():
+        out2 = m.forward(memc, ids.cuda(), None, f['tgt_mask'].cuda())
+        _, per = loss_compute(out2, y.cuda(), norm)
+    with torch.no_grad():
+        lo2 = oracle_loss()
+    if dtype == torch.float32:
+        assert abs(per.item() - lo2.item()) < 1e-3 * abs(lo2.item())
