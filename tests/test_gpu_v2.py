@@ -119,8 +119,16 @@ def test_v2_training_gradients_and_adam_noam(dtype):
             assert abs(loss_node.item() - lo.item()) < tol * abs(lo.item()), (step, loss_node.item(), lo.item())
         if step == 0:                                  # every gradient, first step (identical parameters on both sides)
             err = rel_err if dtype == torch.float32 else l2_err
-            worst = sorted(((err(own[k].grad, v.grad), k) for k, v in leaves.items()), reverse=True)
-            assert worst[0][0] < (5e-4 if dtype == torch.float32 else 1e-1), '\n'.join('%.3e %s' % w for w in worst[:10])
+            gmax = max(v.grad.abs().max().item() for v in leaves.values())
+            # the key-projection biases have a TRUE gradient of zero (softmax is shift invariant): only rounding noise there
+            dead = [k for k in leaves if k.endswith('linear_kv.0.bias')]
+            assert len(dead) == 3 * cfg['layers']
+            for k in dead:
+                assert leaves[k].grad.abs().max().item() < 1e-4 * gmax
+                assert own[k].grad.abs().max().item() < (1e-4 if dtype == torch.float32 else 2e-2) * gmax
+            worst = sorted(((err(own[k].grad, v.grad), k) for k, v in leaves.items() if k not in dead), reverse=True)
+            # bf16: relative L2 per tensor through 2 layers of bf16 activation gradients (d = 32 toy model)
+            assert worst[0][0] < (5e-4 if dtype == torch.float32 else 1.5e-1), '\n'.join('%.3e %s' % w for w in worst[:10])
         assert abs(opt.param_groups[0]['lr'] - ref_opt.param_groups[0]['lr']) < 1e-12
         opt.step()
         sched.step()
