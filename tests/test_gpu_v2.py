@@ -136,8 +136,10 @@ def test_v2_training_gradients_and_adam_noam(dtype):
         ref_sched.step()
         losses.append(loss.item())
     if dtype == torch.float32:
-        worst = max((rel_err(own[k], v.detach()), k) for k, v in leaves.items())
-        assert worst[0] < 2e-3, worst                  # parameters after 3 Adam steps (Adam normalises ~0 gradients: loose)
+        # parameters after 3 Adam steps; the key biases (true gradient 0) take Adam's +-lr steps on rounding noise on both
+        # sides -- the loss does not depend on them -- so they are left out
+        worst = max((rel_err(own[k], v.detach()), k) for k, v in leaves.items() if not k.endswith('linear_kv.0.bias'))
+        assert worst[0] < 2e-3, worst
     # the fast no-grad path sees the updated parameters (cast / table caches key on the version counters)
     with torch.no_grad():
         out2 = m.forward(memc, ids.cuda(), None, f['tgt_mask'].cuda())
