@@ -101,6 +101,28 @@ class ClockSampler(threading.Thread):
                 'samples': len(s)}
 
 
+def bind_to_gpu_numa_node(index):
+    """Pins this rank's threads (and therefore the first-touch placement of the pinned host buffers it allocates next) to
+    the CPU cores NVML reports as local to its GPU -- the launcher's job on a multi-socket host: with all ranks left on
+    node 0, half of them stream their step inputs across the socket interconnect (SCALE_r01: e2e 0.49 of linear at N=8).
+    Returns a short description for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        allowed = os.sched_getaffinity(0)
+        n_words = (max(allowed) // 64) + 1
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        local = {w * 64 + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        use = sorted(local & allowed)
+        if not use:
+            return 'gpu-local cores not in this process\'s cpuset: unchanged (%d cores)' % len(allowed)
+        os.sched_setaffinity(0, use)
+        return 'bound to %d gpu-local cores (%d..%d)' % (len(use), use[0], use[-1])
+    except Exception as e:
+        return 'unchanged (%s)' % type(e).__name__
+
+
 def make_inputs(wl, seed):
     from oracle import synth          # pure torch input generator shared with the tests (no reference code)
     w = WORKLOADS[wl]
@@ -631,6 +653,7 @@ def main():
     from news_image_caption_b200 import DynamicConvDecoder, _lib, build
     from news_image_caption_b200.decoder import random_state_dict
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(local) if world > 1 else 'single process: not bound'
     if world > 1:
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     if rank == 0:
@@ -678,7 +701,7 @@ def main():
         'metric': 'captions_per_sec' if gen_head else 'decoder_tokens_per_sec', 'value': head['value'], 'unit': head['unit'],
         'n_gpus': world, 'steps': head.get('steps', args.steps), 'warmup': args.warmup, 'ms_per_step': head['ms_per_step'],
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
-        'config': {'workload': head['workload'],
+        'config': {'workload': head['workload'], 'host_affinity': numa,
                    'l2': 'per-step working set (K/V 0.5 GB + activations) exceeds the 126 MB L2',
                    'non_pad_tokens_per_step_per_gpu': head.get('non_pad_tokens_per_step_per_gpu')},
         'captions_per_sec': head.get('captions_per_sec', head['value']),

@@ -224,6 +224,7 @@ _SIGS = {
     'tnt_debug_pdl': (None, [i32]),
     'tnt_debug_gemm_tile_n': (None, [i32]),
     'tnt_debug_gemm_stages': (None, [i32]),
+    'tnt_debug_gemm_dynamic': (None, [i32]),
     'tnt_debug_gemm_single_acc': (None, [i32]),
     'tnt_debug_gemm_split_k': (None, [i32]),
     'tnt_debug_force_simt_attention': (None, [i32]),

@@ -23,6 +23,7 @@ constexpr int kAccStride = 256;
 // interleaved accumulators of a single-CTA tile: nacc * BN <= kAccStride columns per accumulator stage
 inline int acc_count(int cg, int bn) { return cg != 1 ? 1 : bn <= 64 ? 4 : bn <= 128 ? 2 : 1; }
 constexpr int kMaxStages = 8;
+constexpr int kSched = 4;                 // depth of the tile-index ring of the dynamic scheduler
 constexpr int kSmemBudget = 220 * 1024;
 
 // tile index -> (m tile, n tile, group).  Tiles are walked in bands of kBandRows output rows: inside a band the m tile
@@ -57,7 +58,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* empty = full + kMaxStages;
   uint64_t* tfull = empty + kMaxStages;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* sfull = tempty + 2;                        // dynamic tile scheduler: tile-index ring, producer -> MMA + epilogue warps
+  uint64_t* sempty = sfull + kSched;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sempty + kSched);
+  volatile int* stile = reinterpret_cast<volatile int*>(tmem_slot + 2);
+  // Tiles are handed out by an atomic counter instead of static striding: a CTA that is not resident yet (its SM is held by
+  // another stream's kernel -- the NCCL all-reduce of the training step's gradient exchange overlaps the backward pass)
+  // simply takes no tile, and the resident CTAs absorb the work.  With static striding every overlapped GEMM waited for the
+  // SMs the collective held: +0.47 ms of kernel time per step at 2 GPUs, +1.1 ms at 8 (tools/trace_train.py).
+  const bool dyn_on = CG == 1 && g.tile_ctr != nullptr;
   float* sbias = reinterpret_cast<float*>(smem + stages * stage_bytes + 512);   // [2 accumulator stages][256], zero padded
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -84,7 +93,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       ptx::mbar_init(&tfull[s], 1);
       ptx::mbar_init(&tempty[s], 4 * CG);              // the leader waits for the epilogue warps of BOTH CTAs
     }
+    for (int s = 0; s < kSched; ++s) {
+      ptx::mbar_init(&sfull[s], 1);
+      ptx::mbar_init(&sempty[s], 5);                   // the MMA warp + 4 epilogue warps have read the slot
+    }
     ptx::fence_barrier_init();
+  }
+  // first tile of this CTA: the counter belongs to this launch alone, so the fetch may run ahead of the PDL wait and its
+  // latency hides behind the barrier initialisation / TMEM allocation
+  int first_tile = 0;
+  if (dyn_on && warp == 0) {
+    if (lane == 0) first_tile = atomicAdd(g.tile_ctr, 1);
+    first_tile = __shfl_sync(0xffffffffu, first_tile, 0);
   }
   if (warp == 2) {
     if (CG == 2) ptx::tmem_alloc_pair<kTmemCols>(tmem_slot);
@@ -113,7 +133,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const bool leader = ptx::elect_one();
       int s = 0;
       uint32_t ph = 0;
-      for (int tile = worker; tile < total_tiles; tile += n_workers) {
+      int ss = 0;
+      uint32_t sph = 0;
+      for (int tile = dyn_on ? first_tile : worker;;) {
+        int next_tile = 0;
+        if (dyn_on) {
+          const int pub = tile < total_tiles ? tile : -1;           // -1: no more tiles
+          ptx::mbar_wait(&sempty[ss], sph ^ 1);
+          if (lane == 0) {
+            stile[ss] = pub;
+            ptx::mbar_arrive(&sfull[ss]);
+          }
+          __syncwarp();
+          if (++ss == kSched) { ss = 0; sph ^= 1; }
+          if (pub < 0) break;
+          if (lane == 0) next_tile = atomicAdd(g.tile_ctr, 1);       // prefetched behind this tile's loads
+        } else if (tile >= total_tiles) {
+          break;
+        }
         int mt, nt, grp;
         decode_tile(tile, m_tiles, n_tiles, kBandRows / BMT, &mt, &nt, &grp);
         const int ga = g.sa ? grp : 0, gw = g.sw ? grp : 0;
@@ -157,6 +194,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           __syncwarp();
           if (++s == stages) { s = 0; ph ^= 1; }
         }
+        tile = dyn_on ? __shfl_sync(0xffffffffu, next_tile, 0) : tile + n_workers;
+      }
+      if (dyn_on && lane == 0) {                       // the last CTA to finish returns the counters to zero for the slot's next user
+        __threadfence();
+        if (atomicAdd(g.tile_ctr + 1, 1) == static_cast<int>(gridDim.x) - 1) {
+          g.tile_ctr[0] = 0;
+          g.tile_ctr[1] = 0;
+          __threadfence();
+        }
       }
     }
     __syncwarp();
@@ -179,9 +225,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t ka = (g.a_mn ? 2048u : UMMA_K * 2u) >> 4, kbs = (g.b_mn ? 2048u : UMMA_K * 2u) >> 4;   // per K step
       const uint32_t stage_step = static_cast<uint32_t>(stage_bytes) >> 4;
       const int nacc = CG == 1 ? g.nacc : 1;
-      int s = 0, it = 0;
+      int s = 0;
       uint32_t ph = 0;
-      for (int tile = worker; tile < total_tiles; tile += n_workers, ++it) {
+      int cs = 0;
+      uint32_t cph = 0;
+      for (int it = 0;; ++it) {
+        if (dyn_on) {
+          ptx::mbar_wait(&sfull[cs], cph);
+          const int t = stile[cs];
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&sempty[cs]);
+          if (++cs == kSched) { cs = 0; cph ^= 1; }
+          if (t < 0) break;
+        } else if (worker + it * n_workers >= total_tiles) {
+          break;
+        }
         const int as = it & 1;
         const uint32_t aph = (it >> 1) & 1;
         ptx::mbar_wait(&tempty[as], aph ^ 1);          // epilogue has drained this accumulator stage
@@ -222,8 +280,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ------------------------------------------------------------ epilogue warps (TMEM -> regs -> HBM)
     const int q = warp & 3;                            // TMEM lane quadrant this warp may read
     const int nacc_e = CG == 1 ? g.nacc : 1;
-    int it = 0;
-    for (int tile = worker; tile < total_tiles; tile += n_workers, ++it) {
+    int cs = 0;
+    uint32_t cph = 0;
+    for (int it = 0;; ++it) {
+      int tile;
+      if (dyn_on) {
+        ptx::mbar_wait(&sfull[cs], cph);
+        tile = stile[cs];
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&sempty[cs]);
+        if (++cs == kSched) { cs = 0; cph ^= 1; }
+        if (tile < 0) break;
+      } else {
+        tile = worker + it * n_workers;
+        if (tile >= total_tiles) break;
+      }
       int mt, nt, grp;
       decode_tile(tile, m_tiles, n_tiles, kBandRows / BMT, &mt, &nt, &grp);
       const int as = it & 1;
@@ -512,6 +583,23 @@ int gemm_tile_n(int dtype, int M, int N) {
   return bn;
 }
 
+// per-launch counter pairs of the dynamic tile scheduler: a static device array, handed out round-robin; a slot comes back
+// after kCtrSlots launches, long after its previous user (same stream, or an earlier step) has reset it
+constexpr int kCtrSlots = 4096;
+__device__ int g_tile_ctrs[2 * kCtrSlots];
+static int* next_tile_ctr() {
+  static int* base[kMaxDevices] = {};
+  static unsigned n = 0;
+  const int dev = cur_device();
+  if (!base[dev]) {
+    void* p = nullptr;
+    if (cudaGetSymbolAddress(&p, g_tile_ctrs) != cudaSuccess) return nullptr;
+    base[dev] = static_cast<int*>(p);
+  }
+  return base[dev] + 2 * (n++ % kCtrSlots);
+}
+static int g_dynamic_tiles = -1;          // -1: TNT_GEMM_DYNAMIC from the environment (default on)
+
 template <int EPI, typename TOut, int CG>
 static int launch_tc_cg(const GemmArgs& g, int BN, cudaStream_t st) {
   CUtensorMap tmA, tmW;
@@ -532,6 +620,12 @@ static int launch_tc_cg(const GemmArgs& g, int BN, cudaStream_t st) {
   if (attr_once.first()) TNT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::kSmemBudget + 4096));
   GemmArgs ga = g;
   ga.nacc = g_single_acc ? 1 : tc::acc_count(CG, BN);
+  if (g_dynamic_tiles < 0) {
+    const char* e = getenv("TNT_GEMM_DYNAMIC");
+    g_dynamic_tiles = (e && e[0] == '0') ? 0 : 1;
+  }
+  // more than one tile per CTA somewhere, or fewer tiles than SMs: either way the counter decides who works
+  ga.tile_ctr = (CG == 1 && g_dynamic_tiles) ? next_tile_ctr() : nullptr;
   TNT_CUDA(launch_pdl(kern, dim3(grid), dim3(tc::kThreads), smem, st, CG, tmA, tmW, ga, BN, stages, n_tiles));
   TNT_LAUNCHED();
   variant_hit(CG == 2 ? V_GEMM_TC_PAIR : V_GEMM_TC_1CTA);
@@ -584,6 +678,7 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
   TNT_CHECK_ARG((epi != EPI_RESIDUAL && epi != EPI_RELU_BWD) || p->residual, "linear: residual epilogue without residual");
   if (p->M == 0) return TNT_OK;
   GemmArgs g;
+  g.tile_ctr = nullptr;
   g.a = p->a; g.w = p->w; g.bias = p->bias; g.res = p->residual; g.c = p->c;
   g.lda = p->lda; g.ldw = p->ldw; g.ldr = p->ldr; g.ldc = p->ldc;
   g.M = p->M; g.N = p->N; g.K = p->K;
@@ -660,6 +755,7 @@ extern "C" int tnt_linear_fwd(const tnt_linear_params* p, tnt_stream stream) {
 }
 extern "C" void tnt_debug_force_simt_gemm(int on) { tnt::gemm_force_simt(on != 0); }
 extern "C" void tnt_debug_gemm_cta_group(int cg) { tnt::g_cta_group = (cg == 1 || cg == 2) ? cg : 0; }
+extern "C" void tnt_debug_gemm_dynamic(int on) { tnt::g_dynamic_tiles = on < 0 ? -1 : (on ? 1 : 0); }
 extern "C" void tnt_debug_gemm_stages(int n) { tnt::g_force_stages = n > 0 ? n : 0; }
 extern "C" void tnt_debug_gemm_single_acc(int on) { tnt::g_single_acc = on ? 1 : 0; }
 extern "C" void tnt_debug_gemm_tile_n(int bn) { tnt::g_force_bn = (bn == 32 || bn == 64 || bn == 128 || bn == 256) ? bn : 0; }

@@ -28,6 +28,9 @@ struct GemmArgs {
   const float* row_lse;
   float gscale;
   const float* row_w;       // optional per-row factor on top of gscale (weighted softmax gradient of the copy heads)
+  // dynamic tile scheduler (single-CTA tcgen05 kernel): tile_ctr[0] = next tile, tile_ctr[1] = CTAs done (both return to 0
+  // when the launch ends); NULL = static striding
+  int* tile_ctr;
   // L2 prefetch hint (weights of the next GEMM of a chain), issued by the prologue
   const char* pf; unsigned long long pf_bytes;
   // dropout on the value the RESIDUAL epilogue adds the residual to / on the RELU epilogue's output (thr == 0: off)
