@@ -124,6 +124,9 @@ int tnt_wn_fold(const float* v, const float* g, void* w_out, int rows, int cols,
 /* bias companion of the GLU interleave: b_out[2j] = b[j], b_out[2j+1] = b[j + n/2] */
 int tnt_glu_interleave_bias(const float* b, float* b_out, int n, tnt_stream stream);
 int tnt_cast(const void* src, void* dst, int64_t n, int dtype_src, int dtype_dst, tnt_stream stream);
+/* the same conversion on at most `max_ctas` CTAs: for casts issued on a side stream while another stream's kernels own the
+ * GPU (the bf16 wire buffers of the gradient exchange, trainer.py) -- a full-width grid stalls that stream for its duration */
+int tnt_cast_background(const void* src, void* dst, int64_t n, int dtype_src, int dtype_dst, int max_ctas, tnt_stream stream);
 
 /* ------------------------------------------------------------------------------------------
  * DynamicConv1dTBC (causal, weight_softmax, padding_l = K-1, no renorm, no bias).

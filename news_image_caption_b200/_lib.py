@@ -152,6 +152,7 @@ _SIGS = {
     'tnt_wn_fold': (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
     'tnt_glu_interleave_bias': (i32, [vp, vp, i32, vp]),
     'tnt_cast': (i32, [vp, vp, i64, i32, i32, vp]),
+    'tnt_cast_background': (i32, [vp, vp, i64, i32, i32, i32, vp]),
     'tnt_dynconv_fwd': (i32, [C.POINTER(DynconvParams), vp]),
     'tnt_dynconv_bwd': (i32, [C.POINTER(DynconvBwdParams), vp]),
     'tnt_dynconv_step': (i32, [C.POINTER(DynconvStepParams), vp]),

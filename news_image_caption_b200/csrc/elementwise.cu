@@ -511,6 +511,45 @@ extern "C" int tnt_glu_interleave_bias(const float* b, float* b_out, int n, tnt_
   return TNT_OK;
 }
 
+namespace tnt {
+namespace {
+// Background form of cast8_kernel: a FEW CTAs, each thread keeping 4 vectors in flight.  The gradient exchange casts on a
+// side stream while the backward pass owns the GPU: a full-width grid (148 x 16 CTAs) stalled the main stream for the
+// length of every cast (50 / 46 / 20 us gaps at each stage, tools/trace_train.py); this one trickles along on <= max_ctas SMs.
+template <typename S, typename D>
+__global__ void __launch_bounds__(256) cast8_bg_kernel(const S* s, D* d, long n8) {
+  const long stride = gridDim.x * 256L;
+  long i = blockIdx.x * 256L + threadIdx.x;
+  for (; i + 3 * stride < n8; i += 4 * stride) {
+    float v[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) load8(s + (i + u * stride) * 8, v[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) store8(d + (i + u * stride) * 8, v[u]);
+  }
+  for (; i < n8; i += stride) {
+    float v[8];
+    load8(s + i * 8, v);
+    store8(d + i * 8, v);
+  }
+}
+}  // namespace
+}  // namespace tnt
+
+extern "C" int tnt_cast_background(const void* src, void* dst, int64_t n, int dtype_src, int dtype_dst, int max_ctas, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(src && dst && n >= 0 && max_ctas > 0, "cast_background: bad arguments");
+  if (n == 0) return TNT_OK;
+  if (dtype_src == dtype_dst || n % 8 != 0 || ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 31) != 0)
+    return tnt_cast(src, dst, n, dtype_src, dtype_dst, stream);
+  const int grid = static_cast<int>(std::min<int64_t>((n / 8 + 255) / 256, max_ctas));
+  cudaStream_t st = as_stream(stream);
+  if (dtype_src == TNT_F32) cast8_bg_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float*>(src), reinterpret_cast<bf16*>(dst), n / 8);
+  else cast8_bg_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const bf16*>(src), reinterpret_cast<float*>(dst), n / 8);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
 extern "C" int tnt_cast(const void* src, void* dst, int64_t n, int dtype_src, int dtype_dst, tnt_stream stream) {
   using namespace tnt;
   TNT_CHECK_ARG(src && dst && n >= 0, "cast: bad arguments");

@@ -32,13 +32,18 @@ def warmup_linear(x, warmup):
     return max((x - 1.0) / (warmup - 1.0), 0.0)
 
 
+CAST_CTAS = int(__import__('os').environ.get('TNT_EXCHANGE_CAST_CTAS', '24'))
+
+
 def _cast(src, dst):
-    """dst <- src across fp32 / bf16 on the current stream: the library's own kernel on the GPU, torch on the CPU (gloo tests)."""
+    """dst <- src across fp32 / bf16 on the current stream: the library's own kernel on the GPU (its background form -- a few
+    CTAs -- because the exchange runs beside the backward pass), torch on the CPU (gloo tests)."""
     if src.is_cuda:
         code = {torch.float32: TNT_F32, torch.bfloat16: TNT_BF16}
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        _lib.check(_lib.lib().tnt_cast(C.c_void_p(src.data_ptr()), C.c_void_p(dst.data_ptr()), src.numel(), code[src.dtype],
-                                       code[dst.dtype], st), 'tnt_cast')
+        ctas = CAST_CTAS if src.numel() > (4 << 20) else 1 << 20       # small slices (the last stage: what trails the backward) at full width
+        _lib.check(_lib.lib().tnt_cast_background(C.c_void_p(src.data_ptr()), C.c_void_p(dst.data_ptr()), src.numel(),
+                                                  code[src.dtype], code[dst.dtype], ctas, st), 'tnt_cast_background')
     else:
         dst.copy_(src)
 

@@ -71,6 +71,32 @@ def main():
         out.append('--- main-stream time overlapped by NCCL kernels: %.3f ms of %.3f ms' % (
             sum(e['dur'] for e in step if e['args'].get('stream') == main_s and overl(e)) / 1e3,
             sum(e['dur'] for e in step if e['args'].get('stream') == main_s) / 1e3))
+        import collections
+        import re
+        agg = collections.OrderedDict()
+        for e in step:
+            if e['args'].get('stream') != main_s:
+                continue
+            nm = re.sub(r'\(.*$', '', e['name'].replace('void ', '')).replace('tnt::', '').replace('(anonymous namespace)::', '')[:70]
+            a = agg.setdefault(nm, [0, 0.0, 0.0])
+            a[0] += 1
+            a[1] += e['dur']
+            if overl(e):
+                a[2] += e['dur']
+        # idle accounting of the main stream: wall - union of its op intervals, and the largest gaps with what follows them
+        ms = sorted((e for e in step if e['args'].get('stream') == main_s), key=lambda e: e['ts'])
+        gaps, end = [], t0
+        for e in ms:
+            if e['ts'] > end:
+                gaps.append((e['ts'] - end, (end - t0) / 1e3, e['name'][:60]))
+            end = max(end, e['ts'] + e['dur'])
+        out.append('--- main stream idle: %.3f ms of %.3f ms wall in %d gaps; gaps > 8 us:' % (sum(g[0] for g in gaps) / 1e3, (t1 - t0) / 1e3, len(gaps)))
+        for g in sorted(gaps, reverse=True)[:30]:
+            if g[0] > 8:
+                out.append('  %7.1f us at +%.3f ms before %s' % g)
+        out.append('--- main-stream kernels: count, total us, us while an NCCL kernel was running')
+        for nm, (c, t, o) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:28]:
+            out.append('  %-72s %4d %9.1f %9.1f' % (nm, c, t, o))
         txt = '\n'.join(out)
         print(txt)
         if len(sys.argv) > 1:
