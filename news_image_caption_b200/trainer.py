@@ -32,7 +32,11 @@ def warmup_linear(x, warmup):
     return max((x - 1.0) / (warmup - 1.0), 0.0)
 
 
-CAST_CTAS = int(__import__('os').environ.get('TNT_EXCHANGE_CAST_CTAS', '24'))
+# measured (2 GPUs, B=64): casting on a FEW CTAs removes the 20-50 us stalls a full-width cast causes at every stage, but the
+# slow casts stretch the exchange chain and compete with the backward for longer: 9.17 ms (full width) vs 9.72 / 10.34 /
+# 10.75 ms at 48 / 24 / 8 CTAs.  Full width stays the default (0); the compute stream's PRIORITY is what keeps the
+# backward ahead of the exchange (Trainer.__init__).
+CAST_CTAS = int(__import__('os').environ.get('TNT_EXCHANGE_CAST_CTAS', '0'))
 
 
 def _cast(src, dst):
@@ -41,7 +45,7 @@ def _cast(src, dst):
     if src.is_cuda:
         code = {torch.float32: TNT_F32, torch.bfloat16: TNT_BF16}
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        ctas = CAST_CTAS if src.numel() > (4 << 20) else 1 << 20       # small slices (the last stage: what trails the backward) at full width
+        ctas = CAST_CTAS if (CAST_CTAS > 0 and src.numel() > (4 << 20)) else 1 << 20
         _lib.check(_lib.lib().tnt_cast_background(C.c_void_p(src.data_ptr()), C.c_void_p(dst.data_ptr()), src.numel(),
                                                   code[src.dtype], code[dst.dtype], ctas, st), 'tnt_cast_background')
     else:
@@ -159,6 +163,12 @@ class Trainer:
         self.exchange = GradientExchange(self.dec.flat_grads, self.dec.stage_slices, group, wire=wire)
         self.group = group
         self.comm_stream = torch.cuda.Stream() if self.exchange.world > 1 else None
+        # multi-GPU: the step itself runs on a HIGH-priority stream, the exchange (casts on comm_stream, NCCL on its own
+        # stream) at the default, lower priority: when SMs free up the block scheduler hands them to the backward pass first,
+        # so the exchange fills in behind it instead of delaying it
+        self.compute_stream = None
+        if self.exchange.world > 1 and __import__('os').environ.get('TNT_COMPUTE_PRIORITY', '1') != '0':
+            self.compute_stream = torch.cuda.Stream(priority=-1)
         self.gscale = torch.ones(1, dtype=torch.float32, device='cuda')
         # multi-GPU: the embedding rows of the tied band tables travel as a packed list (the arena keeps the band tables in
         # stage 0, where their dense softmax part is final); a band whose dim differs from d keeps the dense path
@@ -193,6 +203,16 @@ class Trainer:
     def step(self, prev_target, target, contexts):
         """One optimisation step on this rank's shard.  Returns the GLOBAL [loss_sum (nats), n_tokens] tensor
         (device); the reported loss of the reference is loss_sum / n_tokens / ln 2 (bits per token)."""
+        if self.compute_stream is not None and torch.cuda.current_stream() != self.compute_stream:
+            caller = torch.cuda.current_stream()
+            self.compute_stream.wait_stream(caller)
+            with torch.cuda.stream(self.compute_stream):
+                out = self.step(prev_target, target, contexts)
+            caller.wait_stream(self.compute_stream)
+            for t in list(contexts.values()) + [out]:
+                if torch.is_tensor(t) and t.is_cuda:
+                    t.record_stream(self.compute_stream)
+            return out
         dec, L = self.dec, _lib.lib()
         ids = prev_target['roberta'] if isinstance(prev_target, dict) else prev_target
         self._ensure_sparse(ids.shape[0] * ids.shape[1])
