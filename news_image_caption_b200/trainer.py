@@ -229,22 +229,24 @@ class Trainer:
                 order, wait_on = list(range(n_stages)), {}
             if self.overlap:
                 with torch.cuda.stream(self.comm_stream):
-                    for s in order:
+                    for j, s in enumerate(order):
                         _lib.check(L.tnt_decoder_stream_wait_stage(h, wait_on.get(s, s), C.c_void_p(self.comm_stream.cuda_stream)),
                                    'tnt_decoder_stream_wait_stage')
+                        if j == 0:      # (loss_sum, n_tokens) exist once the forward has ended: exchanged here, off the step's tail
+                            self.exchange.reduce_scalars(out)
                         self.exchange.reduce_slice(s)
                     if self.sparse is not None:
                         self.sparse.gather()
                     self.exchange.finish()
                 cur.wait_stream(self.comm_stream)
             else:
+                self.exchange.reduce_scalars(out)
                 for s in order:
                     self.exchange.reduce_slice(s, async_op=False)
                 if self.sparse is not None:
                     self.sparse.gather()
             if self.sparse is not None:
                 self.sparse.scatter_into(dec.band_table_grads(), dec.embed_padding_idx)
-            self.exchange.reduce_scalars(out)
         # gradient of the reference loss (sum-NLL / n_tokens / ln 2): scale by the global token count on the device
         # (an all-padding global batch has n_tokens == 0: every gradient is 0 then, keep the scale finite)
         torch.reciprocal(out[1:2].clamp_min(1.0) * math.log(2.0), out=self.gscale)
