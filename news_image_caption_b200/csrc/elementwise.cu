@@ -163,6 +163,176 @@ __global__ void __launch_bounds__(kWarps * 32) layernorm_bwd_kernel(tnt_layernor
   }
 }
 
+// C <= 1024, column-owning form: thread j of a 128-thread CTA owns the 8 columns [8j, 8j+8) of R rows at a time, so the
+// gamma / beta gradients are 16 registers per thread (the warp-per-row kernel below keeps 64 + the row itself: 1 CTA of 8
+// warps per SM = 8 rows = 32 KB in flight, 30 % of the HBM peak at 32768 rows).  Here x / dy stay PACKED (bf16) between the
+// two reduction phases: ~140 registers -> 3 CTAs per SM x R = 8 rows = 24 rows (96 KB) in flight per SM.  Row statistics
+// are block reductions over the 4 warps: phase A {sum x, sum dy g}, phase B {sum (x - mean)^2, sum dy g (x - mean)}.
+template <typename T> struct LnPack;
+template <> struct LnPack<bf16> { static constexpr int R = 4; using V = uint4; };
+template <> struct LnPack<float> { static constexpr int R = 4; struct V { float4 a, b; }; };
+__device__ __forceinline__ void ln_unpack(const uint4& u, float (&v)[8]) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+__device__ __forceinline__ void ln_unpack(const LnPack<float>::V& u, float (&v)[8]) {
+  v[0] = u.a.x; v[1] = u.a.y; v[2] = u.a.z; v[3] = u.a.w; v[4] = u.b.x; v[5] = u.b.y; v[6] = u.b.z; v[7] = u.b.w;
+}
+__device__ __forceinline__ void ln_load(const bf16* p, uint4& u) { u = *reinterpret_cast<const uint4*>(p); }
+__device__ __forceinline__ void ln_load(const float* p, LnPack<float>::V& u) {
+  u.a = *reinterpret_cast<const float4*>(p);
+  u.b = *reinterpret_cast<const float4*>(p + 4);
+}
+__device__ __forceinline__ void ln_zero(uint4& u) { u = make_uint4(0, 0, 0, 0); }
+__device__ __forceinline__ void ln_zero(LnPack<float>::V& u) { u.a = u.b = make_float4(0.f, 0.f, 0.f, 0.f); }
+
+// Per-CTA column partials of dgamma / dbeta go to a static scratch, a second tiny kernel sums them: with atomics every one of
+// the 2 C addresses took one atomic from EACH CTA (592-way same-address serialisation at ~80 ns: ~50 us of a 104 us launch at
+// 32768 rows, and the whole 15 -> 47 us at 2048 rows once the CTAs got smaller).  One scratch set per launch parity: launches
+// on ONE stream are serialised anyway; concurrent LayerNorm backward launches on different streams are not supported.
+constexpr int kLnMaxCtas = 1024;
+__device__ float g_ln_scratch[2][kLnMaxCtas * 2 * 1024];
+
+__global__ void __launch_bounds__(256) layernorm_bwd_finish_kernel(const float* scr, int n_ctas, int C, float* dgamma, float* dbeta) {
+  const int i = blockIdx.x * 256 + threadIdx.x;              // column of [dgamma | dbeta]
+  if (i >= 2 * C) return;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  // blockIdx.y takes a slice of the CTAs' partials (one atomic per slice and column: <= 32-way contention)
+  const int per = (n_ctas + gridDim.y - 1) / gridDim.y;
+  int b = blockIdx.y * per;
+  n_ctas = min(n_ctas, b + per);
+  for (; b + 3 < n_ctas; b += 4) {
+    a0 += scr[static_cast<long>(b) * 2 * C + i];
+    a1 += scr[static_cast<long>(b + 1) * 2 * C + i];
+    a2 += scr[static_cast<long>(b + 2) * 2 * C + i];
+    a3 += scr[static_cast<long>(b + 3) * 2 * C + i];
+  }
+  for (; b < n_ctas; ++b) a0 += scr[static_cast<long>(b) * 2 * C + i];
+  const float s = (a0 + a1) + (a2 + a3);
+  atomicAdd(i < C ? dgamma + i : dbeta + (i - C), s);         // the contract: accumulate into zeroed buffers
+}
+
+template <typename T>
+__global__ void __launch_bounds__(128, 3) layernorm_bwd_cols_kernel(tnt_layernorm_bwd_params p, float* scr) {
+  constexpr int R = LnPack<T>::R;
+  using V = typename LnPack<T>::V;
+  __shared__ float redA[4][2 * R], redB[4][2 * R];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const bool act = tid * 8 < p.C;
+  float g[8], dg[8], db[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) g[j] = dg[j] = db[j] = 0.f;
+  if (act) load8(p.gamma + tid * 8, g);
+  const float invC = 1.f / p.C;
+  auto fetch = [&](int row0, V (&xv)[R], V (&dv)[R]) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (act && row0 + r < p.rows) {
+        ln_load(reinterpret_cast<const T*>(p.x) + static_cast<long>(row0 + r) * p.ldx + tid * 8, xv[r]);
+        ln_load(reinterpret_cast<const T*>(p.dy) + static_cast<long>(row0 + r) * p.lddy + tid * 8, dv[r]);
+      } else {
+        ln_zero(xv[r]);
+        ln_zero(dv[r]);
+      }
+    }
+  };
+  V xr[R], dr[R], xn[R], dn[R];
+  fetch(blockIdx.x * R, xr, dr);
+  for (int row0 = blockIdx.x * R; row0 < p.rows; row0 += gridDim.x * R) {
+    // the NEXT batch's rows are requested before this batch's reductions: loads stay in flight through the two barriers
+    fetch(row0 + gridDim.x * R, xn, dn);
+    // ---- phase A: sum x, sum dy*g per row
+    float sa[2 * R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      float x[8], d[8];
+      ln_unpack(xr[r], x);
+      ln_unpack(dr[r], d);
+      float a = 0.f, c = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        a += x[j];
+        c = fmaf(d[j], g[j], c);
+      }
+      sa[r] = a;
+      sa[R + r] = c;
+    }
+#pragma unroll
+    for (int i = 0; i < 2 * R; ++i) sa[i] = warp_sum(sa[i]);
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 2 * R; ++i) redA[warp][i] = sa[i];
+    }
+    __syncthreads();
+    float mean[R], s1[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      mean[r] = (redA[0][r] + redA[1][r] + redA[2][r] + redA[3][r]) * invC;
+      s1[r] = (redA[0][R + r] + redA[1][R + r] + redA[2][R + r] + redA[3][R + r]) * invC;
+    }
+    // ---- phase B: sum (x - mean)^2, sum dy*g*(x - mean)
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      float x[8], d[8];
+      ln_unpack(xr[r], x);
+      ln_unpack(dr[r], d);
+      float b = 0.f, e = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xc = act ? x[j] - mean[r] : 0.f;
+        b = fmaf(xc, xc, b);
+        e = fmaf(d[j] * g[j], xc, e);
+      }
+      sa[r] = b;
+      sa[R + r] = e;
+    }
+#pragma unroll
+    for (int i = 0; i < 2 * R; ++i) sa[i] = warp_sum(sa[i]);
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 2 * R; ++i) redB[warp][i] = sa[i];
+    }
+    __syncthreads();
+    // ---- dx, and the column partials of dgamma / dbeta
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float ssq = redB[0][r] + redB[1][r] + redB[2][r] + redB[3][r];
+      const float e = redB[0][R + r] + redB[1][R + r] + redB[2][R + r] + redB[3][R + r];
+      const float sdev = sqrtf(ssq / (p.C - 1));
+      const float rstd = p.variant == 1 ? 1.f / (sdev + p.eps) : rsqrtf(ssq * invC + p.eps);
+      const float s2 = rstd * e;                                   // sum dxhat * xhat
+      const float c2 = p.variant == 1 ? (sdev > 0.f ? s2 / ((p.C - 1) * sdev) : 0.f) : rstd * s2 * invC;
+      if (act && row0 + r < p.rows) {
+        float x[8], d[8], o[8];
+        ln_unpack(xr[r], x);
+        ln_unpack(dr[r], d);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float xh = (x[j] - mean[r]) * rstd;
+          o[j] = rstd * (d[j] * g[j] - s1[r]) - xh * c2;
+          dg[j] = fmaf(d[j], xh, dg[j]);
+          db[j] += d[j];
+        }
+        store8(reinterpret_cast<T*>(p.dx) + static_cast<long>(row0 + r) * p.lddx + tid * 8, o);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      xr[r] = xn[r];
+      dr[r] = dn[r];
+    }
+  }
+  if (act) {
+    float* mine = scr + static_cast<long>(blockIdx.x) * 2 * p.C + tid * 8;
+    store8(mine, dg);
+    store8(mine + p.C, db);
+  }
+}
+
 // C <= 1024: the row (x, dy) lives in registers -- one HBM read of each, no re-reads -- and every lane keeps the
 // dgamma / dbeta partials of ITS 32 channels in registers across all rows of its warp; the block combines the warps'
 // partials through shared memory once at the end (the generic kernel above issues 2*C shared atomics per row).
@@ -443,7 +613,29 @@ extern "C" int tnt_layernorm_bwd(const tnt_layernorm_bwd_params* p, tnt_stream s
   if (p->rows == 0) return TNT_OK;
   const int grid = std::min((p->rows + kWarps - 1) / kWarps, 2 * num_sms());
   const size_t smem = 2 * static_cast<size_t>(p->C) * 4;
-  if (p->C <= 1024) {
+  static const bool cols_on = [] { const char* e = getenv("TNT_LN_BWD_COLS"); return !(e && e[0] == '0'); }();
+  if (cols_on && p->C <= 1024 && aligned16(p->x) && aligned16(p->dy) && aligned16(p->dx) && p->ldx % 8 == 0 && p->lddy % 8 == 0 &&
+      p->lddx % 8 == 0 && (reinterpret_cast<uintptr_t>(p->gamma) & 15) == 0) {
+    const int R = 4;
+    static const int per_sm_c = [] { const char* e = getenv("TNT_LN_BWD_COLS_CTAS_PER_SM"); return e ? std::max(1, atoi(e)) : 3; }();
+    const int grid_c = std::min(std::min((p->rows + R - 1) / R, per_sm_c * num_sms()), kLnMaxCtas);
+    static float* scr_base[kMaxDevices] = {};
+    static unsigned parity = 0;
+    const int dev = cur_device();
+    if (!scr_base[dev]) {
+      void* sp = nullptr;
+      TNT_CUDA(cudaGetSymbolAddress(&sp, g_ln_scratch));
+      scr_base[dev] = static_cast<float*>(sp);
+    }
+    float* scr = scr_base[dev] + static_cast<size_t>(parity++ & 1) * kLnMaxCtas * 2 * 1024;
+    if (p->dtype == TNT_BF16) layernorm_bwd_cols_kernel<bf16><<<grid_c, 128, 0, as_stream(stream)>>>(*p, scr);
+    else layernorm_bwd_cols_kernel<float><<<grid_c, 128, 0, as_stream(stream)>>>(*p, scr);
+    TNT_LAUNCHED();
+    static const bool skip_finish = [] { const char* e = getenv("TNT_LN_BWD_SKIP_FINISH"); return e && e[0] == '1'; }();   // timing diagnosis only
+    if (!skip_finish)
+      layernorm_bwd_finish_kernel<<<dim3((2 * p->C + 255) / 256, std::min(32, (grid_c + 15) / 16)), 256, 0, as_stream(stream)>>>(
+          scr, grid_c, p->C, p->dgamma, p->dbeta);
+  } else if (p->C <= 1024) {
     const size_t smem_s = static_cast<size_t>(kWarps) * 2 * p->C * 4;           // <= 64 KB
     // every CTA ends with 2*C atomics onto dgamma / dbeta: few CTAs with several rows per warp beat one row per warp
     static const int per_sm = [] { const char* e = getenv("TNT_LN_BWD_CTAS_PER_SM"); return e ? std::max(1, atoi(e)) : 4; }();
