@@ -146,6 +146,55 @@ class DynamicConv1dTBC(nn.Module):
             incremental_state[self._key()] = buf.index_select(1, new_order)
 
 
+class LightweightConv1dTBC(nn.Module):
+    """lightweight.py:86-253 (`decoder_conv_type: lightweight`, decoder_flattened.py:226-230): the same causal depthwise
+    convolution as DynamicConv1dTBC with STATIC taps -- one learnable [num_heads, 1, K] weight, soft-maxed over K, shared by
+    every timestep and caption.  It is the DynamicConv kernel fed with the weight broadcast as its tap logits (forward and
+    backward: autograd's expand sums the per-position tap gradients into the weight).  Supported configuration = what the
+    decoder builds: weight_softmax=True, padding_l = kernel_size - 1."""
+
+    def __init__(self, input_size, kernel_size=1, padding_l=None, num_heads=1, weight_dropout=0., weight_softmax=False,
+                 bias=False):
+        super().__init__()
+        if not weight_softmax:
+            raise NotImplementedError('LightweightConv1dTBC: only weight_softmax=True is implemented')
+        if padding_l is not None and padding_l != kernel_size - 1:
+            raise NotImplementedError('LightweightConv1dTBC: causal padding_l = kernel_size - 1 only')
+        self.input_size, self.kernel_size, self.num_heads = input_size, kernel_size, num_heads
+        self.weight_dropout = weight_dropout
+        self.weight = nn.Parameter(torch.empty(num_heads, 1, kernel_size))
+        nn.init.xavier_uniform_(self.weight)
+        self.bias = nn.Parameter(torch.zeros(input_size)) if bias else None
+        _INSTANCE_ID[0] += 1
+        self._id = _INSTANCE_ID[0]
+
+    def _key(self):
+        return '%s.%d.%s' % (type(self).__name__, self._id, 'input_buffer')
+
+    def forward(self, x, incremental_state=None, unfold=False):
+        """x [T, B, C] -> [T, B, C]; `unfold` accepted and ignored (one algorithm for both reference paths)."""
+        T, B, _ = x.shape
+        drop = None
+        if self.training and self.weight_dropout > 0:
+            if incremental_state is not None:
+                raise NotImplementedError('LightweightConv1dTBC: weight_dropout on the incremental path')
+            drop = (self.weight_dropout, _draw_seed(), self._id)
+        logits = self.weight.view(1, 1, -1).expand(T, B, self.num_heads * self.kernel_size).to(x.dtype)
+        hist = None
+        if incremental_state is not None:
+            hist = incremental_state.get(self._key())
+            window = x if hist is None else torch.cat([hist, x], 0)
+            keep = self.kernel_size - 1
+            incremental_state[self._key()] = window[-keep:].detach() if keep > 0 else window[:0]
+        y = DynConvFn.apply(x, logits, self.num_heads, self.kernel_size, hist, drop)
+        return y if self.bias is None else y + self.bias.to(y.dtype).view(1, 1, -1)
+
+    def reorder_incremental_state(self, incremental_state, new_order):
+        buf = incremental_state.get(self._key())
+        if buf is not None:
+            incremental_state[self._key()] = buf.index_select(1, new_order)
+
+
 class XattnFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, q, k, v, H, scale, pad_mask, mask_S, need_weights, drop=None):

@@ -123,6 +123,20 @@ def dynamic_conv(x: torch.Tensor, w_tap: torch.Tensor, H: int, K: int, tap_drop=
     return y.reshape(T, B, C)
 
 
+def lightweight_conv(x: torch.Tensor, weight: torch.Tensor, H: int, K: int, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """LightweightConv1dTBC (padding_l = K-1, weight_softmax) -- ttl/tell/modules/convolutions/lightweight.py:149-220:
+    softmax over the K static taps of every head (in fp32, :174-175 / :193-194), the same taps for every timestep and
+    caption, zero padding on the left (taps reaching before t = 0 dropped after the softmax, :201-203), optional bias (:145-146).
+    weight [H, 1, K]."""
+    T, B, C = x.shape
+    R = C // H
+    w = F.softmax(weight.view(H, K).float(), dim=1).type_as(weight)
+    xp = F.pad(x, (0, 0, 0, 0, K - 1, 0))
+    win = xp.unfold(0, K, 1)                              # [T,B,C,K]
+    y = torch.einsum('tbhrk,hk->tbhr', win.reshape(T, B, H, R, K), w).reshape(T, B, C)
+    return y if bias is None else y + bias.view(1, 1, -1)
+
+
 def dynamic_conv_step(x_new: torch.Tensor, hist: Optional[torch.Tensor], w_tap: torch.Tensor,
                       H: int, K: int):
     """Incremental DynamicConv -- dynamic.py:95-99,114-116: keep the last K-1 conv inputs,

@@ -179,3 +179,35 @@ def test_attention_score_forward(M, separate, bias_row, zero_row, dtype, tol):
     with pytest.raises(NotImplementedError):
         M.multi_head_attention_score_forward(q.cuda(), mem.cuda(), E, H, wc, b.cuda(), None, False, 0.0,
                                              attn_mask=torch.zeros(T, S).cuda())
+
+
+@pytest.mark.parametrize('dtype,tol', [(torch.float32, 1e-5), (torch.bfloat16, 2e-2)])
+def test_lightweight_conv_module(M, dtype, tol):
+    """LightweightConv1dTBC drop-in (lightweight.py:86-253; `decoder_conv_type: lightweight`): forward, gradients w.r.t. the
+    input and the static [H, 1, K] weight, bias, K > T, and the incremental buffer, against the oracle (pinned on the
+    unmodified module: test_lightweight_conv_matches_reference)."""
+    g = torch.Generator().manual_seed(3)
+    for T, K in ((11, 7), (3, 15)):
+        B, C, H = 3, 64, 4
+        m = M.LightweightConv1dTBC(C, K, padding_l=K - 1, num_heads=H, weight_softmax=True, bias=True).cuda().eval()
+        assert sorted(m.state_dict().keys()) == ['bias', 'weight'] and tuple(m.weight.shape) == (H, 1, K)
+        with torch.no_grad():
+            m.bias.normal_(generator=None)
+        x = torch.randn(T, B, C, generator=g)
+        w = m.weight.detach().cpu().clone().requires_grad_(True)
+        xr = x.clone().requires_grad_(True)
+        yo = O.lightweight_conv(xr, w, H, K, m.bias.detach().cpu())
+        gy = torch.randn(T, B, C, generator=g)
+        yo.backward(gy)
+        xc = x.cuda().to(dtype).requires_grad_(True)
+        y = m(xc)
+        y.backward(gy.cuda().to(dtype))
+        assert rel_err(y, yo.detach()) < tol
+        assert rel_err(xc.grad, xr.grad) < max(tol, 1e-4) and rel_err(m.weight.grad, w.grad) < max(5 * tol, 1e-4)
+        if dtype == torch.float32:
+            state = {}
+            with torch.no_grad():
+                steps = torch.cat([m(x[t:t + 1].cuda(), incremental_state=state) for t in range(T)], 0)
+            assert rel_err(steps, yo.detach()) < 1e-5
+            key = [k for k in state if k.endswith('input_buffer')][0]
+            assert key.startswith('LightweightConv1dTBC.') and state[key].shape[0] == min(K - 1, T)

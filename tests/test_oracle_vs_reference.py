@@ -416,3 +416,28 @@ def test_module_generate_loop_around_reference_decoder(nsrc, srcs):
     assert ids_m.shape == ids_o.shape and torch.equal(ids_m, ids_o)
     close(lp_o, lp_m)
     torch.set_grad_enabled(True)
+
+
+@pytest.mark.parametrize('T,K,unfold', [(9, 5, False), (9, 5, True), (3, 7, False)])
+def test_lightweight_conv_matches_reference(T, K, unfold):
+    """O.lightweight_conv against the unmodified LightweightConv1dTBC (lightweight.py:86-253), both of its paths
+    (band-matrix and unfolded) incl. K > T, with bias, and gradients."""
+    install = ri.load_tell()          # stubs + imports
+    del install
+    import tell.modules as M
+    torch.manual_seed(5)
+    B, C, H = 3, 24, 4
+    m = M.LightweightConv1dTBC(C, K, padding_l=K - 1, num_heads=H, weight_softmax=True, bias=True).eval()
+    with torch.no_grad():
+        m.bias.normal_()
+    x = torch.randn(T, B, C, requires_grad=True)
+    y = m(x, unfold=unfold)
+    gy = torch.randn_like(y)
+    gx, gw = torch.autograd.grad(y, [x, m.weight], gy)
+    x2 = x.detach().clone().requires_grad_(True)
+    w2 = m.weight.detach().clone().requires_grad_(True)
+    yo = O.lightweight_conv(x2, w2, H, K, m.bias.detach())
+    gx2, gw2 = torch.autograd.grad(yo, [x2, w2], gy)
+    close(yo, y.detach())
+    close(gx2, gx)
+    close(gw2, gw)
