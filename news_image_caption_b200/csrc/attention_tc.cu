@@ -46,6 +46,7 @@ struct Args {
   const uint32_t* tile_live;                      // optional [B]: bit i set = key tile i of batch row b holds an un-masked key
   float* weights;                                 // optional [B, T, S] fp32, ZEROED by the launcher: head-averaged probabilities
   float inv_heads;                                //   (multi_head.py:478-482), accumulated with red.global.add by a third pass
+  long m_stride_t;                                // D128 / V2 mask: byte stride over the query index (0 = one mask row per batch entry)
 };
 
 // Work list in shared memory: entry = batch row | (key tiles to visit) << 16.  Tiles whose keys are all padding contribute
@@ -95,7 +96,15 @@ __device__ __forceinline__ float redux_max(float v) {
 }
 __device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
-template <bool DROP>      // dropout on the probabilities compiled in only for the training step (zero cost for inference)
+// DROP: dropout on the probabilities, compiled in only for the training step (zero cost for inference).
+// D128: ONE head of 128 dims per item instead of a pair of 64-dim heads -- the `final*` model (8 heads of 128,
+// final_roberta2/transformer_v2.py:224-266).  In memory a 128-dim head is the same two 64-column boxes as a head pair, so the
+// TMA traffic, the V^T operand of the PV product (two 64-channel atoms) and the O^T epilogue carry over; the score product
+// accumulates both 64-column halves into ONE 32-query accumulator (8 k-steps), only the first four softmax warps have
+// scores to work on (the other four keep their half of P at zero and join the barriers), and the mask follows
+// attention() of transformer_v2.py:213-222: mask[b, t, s] == 0 -> the score is REPLACED by -1e9 (a fully masked row
+// becomes uniform over the S keys, it is not dropped), one validity bit per (key, query).
+template <bool DROP, bool D128>
 __global__ void __launch_bounds__(kThreads, 1)
 xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, Args a) {
@@ -136,7 +145,15 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = bar->tmem;
-  const int HP = a.H >> 1;
+  const int HP = D128 ? a.H : a.H >> 1;      // head slots per batch entry: single 128-dim heads or pairs of 64-dim heads
+  if (D128) {                        // the second head's half of every P stage stays zero for the whole kernel
+    for (int i = threadIdx.x; i < PS * TKEYS * 4; i += kThreads) {
+      const int st = i / (TKEYS * 4), r = (i / 4) % TKEYS, j = i & 3;
+      *reinterpret_cast<uint4*>(sP + st * P_STAGE + r * 128 + ((4 + j) ^ (r & 7)) * 16) = make_uint4(0, 0, 0, 0);
+    }
+    ptx::fence_proxy_async();
+    __syncthreads();
+  }
   pdl_wait();                       // prologue above overlaps the preceding kernel's tail (PDL)
 
   if (warp == 0) {
@@ -201,7 +218,8 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             for (int k = 0; k < D / 16; ++k) {
               const uint64_t ad = ptx::umma_smem_desc(k_addr + h * TKEYS * 128 + k * 32, 16, 1024);
               const uint64_t bd = ptx::umma_smem_desc(q_addr + h * TQ * 128 + k * 32, 16, 1024);
-              if (leader) ptx::umma_bf16_ss(tmem + i * 64 + h * 32, ad, bd, idesc_qk, k != 0);
+              // pair of heads: one accumulator per head; one 128-dim head: both 64-column halves into the same accumulator
+              if (leader) ptx::umma_bf16_ss(tmem + i * 64 + (D128 ? 0 : h * 32), ad, bd, idesc_qk, D128 ? (h | k) != 0 : k != 0);
             }
           }
           if (leader) ptx::umma_commit(&bar->k_empty[ks]);
@@ -250,29 +268,50 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const uint32_t live = ent >> 16;
       // validity of this lane's key in every tile (key-padding mask: multi_head.py:441-449)
       const int nl = __popc(live);
-      uint32_t valid = 0;             // bit j: this lane's key of the j-th LIVE tile takes part
+      const bool score_warp = !D128 || hd == 0;      // D128: the second group of four warps has no score columns
+      uint32_t valid = 0;             // bit j: this lane's key of the j-th LIVE tile takes part (D128: lies inside [0, S))
+      uint32_t vis[D128 ? MAX_TILES : 1];            // D128: bit c of vis[j] = query c of this tile SEES the key (mask != 0)
       {
         int j = 0;
         for (uint32_t m = live; m; m &= m - 1, ++j) {
           const int key = (__ffs(m) - 1) * TKEYS + quad * 32 + lane;
           bool ok = key < a.S;
-          if (ok && a.mask && key < a.mask_S) ok = a.mask[static_cast<long>(b) * a.m_stride_b + key] == 0;
+          if (D128) {
+            uint32_t w = 0xFFFFFFFFu;
+            if (ok && a.mask && score_warp) {
+              const uint8_t* mp = a.mask + static_cast<long>(b) * a.m_stride_b + key;
+              if (a.m_stride_t == 0) {
+                w = mp[0] ? 0xFFFFFFFFu : 0u;
+              } else {
+                w = 0;
+                for (int c = 0; c < TQ; ++c) {
+                  const int t = min(qt * TQ + c, a.T - 1);
+                  w |= static_cast<uint32_t>(mp[static_cast<long>(t) * a.m_stride_t] != 0) << c;
+                }
+              }
+            }
+            vis[j] = w;
+          } else if (ok && a.mask && key < a.mask_S) {
+            ok = a.mask[static_cast<long>(b) * a.m_stride_b + key] == 0;
+          }
           valid |= static_cast<uint32_t>(ok) << j;
         }
       }
+      const float neg_raw = -1e9f / a.scale;         // raw-score value whose scaled form is the reference's -1e9 fill
       ptx::mbar_wait(&bar->s_ready, par);
       ptx::tc_fence_after();
       // ---- pass 1: column maxima over the keys
       float mx[32];
 #pragma unroll
       for (int c = 0; c < 32; ++c) mx[c] = -INFINITY;
-      for (int i = 0; i < nl; ++i) {
+      for (int i = 0; i < nl && score_warp; ++i) {
         uint32_t v[32];
         ptx::tmem_ld_32x32(tmem + lane_base + i * 64 + hd * 32, v);
         ptx::tmem_ld_wait();
         if ((valid >> i) & 1) {
 #pragma unroll
-          for (int c = 0; c < 32; ++c) mx[c] = fmaxf(mx[c], __uint_as_float(v[c]));
+          for (int c = 0; c < 32; ++c)
+            mx[c] = fmaxf(mx[c], (!D128 || ((vis[D128 ? i : 0] >> c) & 1)) ? __uint_as_float(v[c]) : neg_raw);
         }
       }
       float mine = -INFINITY;
@@ -299,10 +338,22 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       uint32_t mleft = live;
       for (int i = 0; i < nl; ++i, mleft &= mleft - 1) {
         const int tile = __ffs(mleft) - 1;                    // key tile the i-th score tile belongs to
+        if (!score_warp) {                                    // D128: nothing to write (this half of P is zero); keep the ring in step
+          ptx::mbar_wait(&bar->p_empty[ps], pph ^ 1);
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&bar->p_ready[ps]);
+          if (++ps == PS) { ps = 0; pph ^= 1; }
+          continue;
+        }
         uint32_t v[32];
         ptx::tmem_ld_32x32(tmem + lane_base + i * 64 + hd * 32, v);
         ptx::tmem_ld_wait();
         const bool ok = (valid >> i) & 1;
+        if (D128) {                                            // masked (query, key) pairs carry the -1e9 fill, not "absent"
+#pragma unroll
+          for (int c = 0; c < 32; ++c)
+            if (!((vis[D128 ? i : 0] >> c) & 1)) v[c] = __float_as_uint(neg_raw);
+        }
         uint32_t pk[16];
 #pragma unroll
         for (int c = 0; c < 32; c += 2) {
@@ -380,22 +431,23 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const float* rsl = red + 256 + hd * 128;
         const float l = rsl[lane] + rsl[32 + lane] + rsl[64 + lane] + rsl[96 + lane];
         const int t = qt * TQ + lane;
-        if (t < a.T) a.lse[(static_cast<long>(b) * a.H + hp * 2 + hd) * a.T + t] = l > 0.f ? col_max * a.scale + __logf(l) : INFINITY;
+        if (t < a.T && score_warp)
+          a.lse[(static_cast<long>(b) * a.H + (D128 ? hp : hp * 2 + hd)) * a.T + t] = l > 0.f ? col_max * a.scale + __logf(l) : INFINITY;
       }
       // ---- epilogue: O^T rows of this quadrant belong to head (quad / 2); this warp takes 16 queries
-      const int oh = quad >> 1;
+      const int oh = D128 ? 0 : quad >> 1;
       const int q0 = hd * 16;
       ptx::mbar_wait(&bar->o_ready, par);
       ptx::tc_fence_after();
       uint32_t o[16];
-      ptx::tmem_ld_32x16(tmem + lane_base + O_COL + oh * 32 + q0, o);
+      ptx::tmem_ld_32x16(tmem + lane_base + O_COL + oh * 32 + q0, o);      // D128: O^T columns 0..31 = the 32 queries
       ptx::tmem_ld_wait();
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&bar->o_empty);
       const float* rs = red + 256 + oh * 128;
-      const int dch = (quad & 1) * 32 + lane;                     // channel inside the head
-      bf16* out = reinterpret_cast<bf16*>(a.out) + static_cast<long>(b) * a.o_stride_b + (hp * 2 + oh) * D + dch;
+      const int dch = D128 ? quad * 32 + lane : (quad & 1) * 32 + lane;      // channel inside the head
+      bf16* out = reinterpret_cast<bf16*>(a.out) + static_cast<long>(b) * a.o_stride_b + (D128 ? hp * 2 * D : (hp * 2 + oh) * D) + dch;
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
         const int q = q0 + j, t = qt * TQ + q;
@@ -427,8 +479,16 @@ int xattn_tile_mask(const uint8_t* mask, long m_stride_b, int B, int S, int mask
 }
 
 bool xattn_tc_supported(const tnt_xattn_params* p) {
-  if (p->dtype != TNT_BF16 || p->D != 64 || (p->H & 1) || p->n_extra != 0 || p->kv_group > 1) return false;
-  if (p->mask_mode != TNT_MASK_NONE && p->mask_mode != TNT_MASK_KEY_PADDING) return false;
+  if (p->dtype != TNT_BF16 || p->n_extra != 0 || p->kv_group > 1) return false;
+  if (p->D == 128) {
+    // the final* model: one 128-dim head per item, transformer_v2's `mask == 0 -> -1e9` rule; no weights / LSE / dropout
+    static const bool d128_on = [] { const char* e = getenv("TNT_XATTN_TC_D128"); return !(e && e[0] == '0'); }();
+    if (!d128_on || p->weights || p->lse || p->drop.p > 0.f || p->tile_live) return false;
+    if (p->mask_mode != TNT_MASK_NONE && p->mask_mode != TNT_MASK_V2) return false;
+  } else {
+    if (p->D != 64 || (p->H & 1)) return false;
+    if (p->mask_mode != TNT_MASK_NONE && p->mask_mode != TNT_MASK_KEY_PADDING) return false;
+  }
   if (p->S < 1 || p->S > atc::MAX_TILES * atc::TKEYS) return false;
   const long strides = p->q_stride_t | p->q_stride_b | p->k_stride_s | p->k_stride_b | p->v_stride_s | p->v_stride_b;
   return (strides % 8) == 0 && aligned16(p->q) && aligned16(p->k) && aligned16(p->v);
@@ -441,8 +501,10 @@ int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st) {
   TNT_TRY(make_tmap_bf16_3d(&tmK, p->k, E, p->B, p->S, p->k_stride_b, p->k_stride_s, 64, 1, atc::TKEYS));
   TNT_TRY(make_tmap_bf16_3d(&tmV, p->v, E, p->B, p->S, p->v_stride_b, p->v_stride_s, 64, 1, atc::TKEYS));
   atc::Args a;
-  a.mask = p->mask_mode == TNT_MASK_KEY_PADDING ? p->mask : nullptr;
+  const bool d128 = p->D == 128;
+  a.mask = (p->mask_mode == TNT_MASK_KEY_PADDING || p->mask_mode == TNT_MASK_V2) ? p->mask : nullptr;
   a.m_stride_b = p->m_stride_b;
+  a.m_stride_t = p->m_stride_t;
   a.out = p->out; a.o_stride_t = p->o_stride_t; a.o_stride_b = p->o_stride_b;
   a.B = p->B; a.T = p->T; a.S = p->S; a.H = p->H;
   a.mask_S = p->mask_S > 0 ? p->mask_S : p->S;
@@ -455,18 +517,21 @@ int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st) {
   // the kernel accumulates the weights with reductions (and never visits all-padding tiles): start from zero
   if (p->weights) TNT_CUDA(cudaMemsetAsync(p->weights, 0, sizeof(float) * static_cast<size_t>(p->B) * p->T * p->S, st));
   a.n_qt = (p->T + atc::TQ - 1) / atc::TQ;
-  a.n_items = p->B * (p->H / 2) * a.n_qt;
+  a.n_items = p->B * (d128 ? p->H : p->H / 2) * a.n_qt;
   a.n_tiles = (p->S + atc::TKEYS - 1) / atc::TKEYS;
   static PerDeviceOnce attr_once;
   if (attr_once.first()) {
-    TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
-    TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
+    TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
+    TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
+    TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
   }
   const int grid = std::min(a.n_items, num_sms());
-  if (a.drop.thr)
-    TNT_CUDA(launch_pdl(atc::xattn_tc_kernel<true>, dim3(grid), dim3(atc::kThreads), atc::SMEM_BYTES, st, 1, tmQ, tmK, tmV, a));
+  if (d128)
+    TNT_CUDA(launch_pdl(atc::xattn_tc_kernel<false, true>, dim3(grid), dim3(atc::kThreads), atc::SMEM_BYTES, st, 1, tmQ, tmK, tmV, a));
+  else if (a.drop.thr)
+    TNT_CUDA(launch_pdl(atc::xattn_tc_kernel<true, false>, dim3(grid), dim3(atc::kThreads), atc::SMEM_BYTES, st, 1, tmQ, tmK, tmV, a));
   else
-    TNT_CUDA(launch_pdl(atc::xattn_tc_kernel<false>, dim3(grid), dim3(atc::kThreads), atc::SMEM_BYTES, st, 1, tmQ, tmK, tmV, a));
+    TNT_CUDA(launch_pdl(atc::xattn_tc_kernel<false, false>, dim3(grid), dim3(atc::kThreads), atc::SMEM_BYTES, st, 1, tmQ, tmK, tmV, a));
   TNT_LAUNCHED();
   return TNT_OK;
 }

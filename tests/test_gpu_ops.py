@@ -481,3 +481,47 @@ def test_nan_mask(ops, dtype):
         out, m = ops.nan_mask(x.cuda())
         assert torch.equal(m.cpu(), mref)
         assert torch.equal(out.float().cpu(), ref)           # pure copy / zero fill: bit exact
+
+
+@pytest.mark.parametrize('case', ['key_mask', 'causal', 'no_mask'])
+def test_xattn_tc_head_dim_128_v2_mask(case):
+    """The `final*` attention (8 heads of 128, attention() of final_roberta2/transformer_v2.py:213-222: mask == 0 -> -1e9) on
+    the tcgen05 kernel's D = 128 instantiation against fp32 torch on the CPU and against the SIMT kernel: per-key article
+    masks incl. a FULLY masked caption (uniform attention, not zero), the causal [B, T, T] self-attention mask over two query
+    tiles, three key tiles with a ragged tail, and the unmasked image attention."""
+    import math
+    from news_image_caption_b200 import _lib, build, ops
+    build.build()
+    L = _lib.lib()
+    g = torch.Generator().manual_seed(11)
+    B, H, D = 3, 8, 128
+    E = H * D
+    T, S = (40, 40) if case == 'causal' else (40, 300)
+    q = (torch.randn(T, B, E, generator=g) * 0.5).bfloat16()
+    k = (torch.randn(B, S, E, generator=g) * 0.5).bfloat16()
+    v = torch.randn(B, S, E, generator=g).bfloat16()
+    mask = None
+    if case == 'key_mask':
+        mask = torch.rand(B, 1, S, generator=g) > 0.3
+        mask[1] = False                                      # nothing visible: softmax over -1e9 everywhere = uniform
+    elif case == 'causal':
+        mask = torch.tril(torch.ones(1, T, T, dtype=torch.bool)).expand(B, T, T).clone()
+    qf = q.float().view(T, B, H, D).permute(1, 2, 0, 3)
+    kf = k.float().view(B, S, H, D).permute(0, 2, 1, 3)
+    vf = v.float().view(B, S, H, D).permute(0, 2, 1, 3)
+    s = qf @ kf.transpose(-1, -2) / math.sqrt(D)
+    if mask is not None:
+        s = s.masked_fill(mask[:, None] == 0, -1e9)
+    want = (torch.softmax(s, -1) @ vf).permute(2, 0, 1, 3).reshape(T, B, E)
+    n0 = L.tnt_variant_count(b'xattn.tc')
+    args = (q.cuda(), (B * E, E), k.cuda(), (E, S * E), v.cuda(), (E, S * E), B, T, S, H, D, 1.0 / math.sqrt(D))
+    out = ops.xattn_strided(*args, v2_mask=mask.cuda() if mask is not None else None)
+    torch.cuda.synchronize()
+    assert L.tnt_variant_count(b'xattn.tc') == n0 + 1          # the tcgen05 kernel ran
+    assert rel_err(out, want) < 2e-2
+    L.tnt_debug_force_simt_attention(1)
+    try:
+        ref = ops.xattn_strided(*args, v2_mask=mask.cuda() if mask is not None else None)
+    finally:
+        L.tnt_debug_force_simt_attention(0)
+    assert rel_err(out, ref) < 2e-2
