@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, 'libtnt_b200.so')
+LIB_PATH = os.environ.get('TNT_B200_LIB') or os.path.join(HERE, 'libtnt_b200.so')     # (override: A/B of two builds)
 
 TNT_F32, TNT_BF16 = 0, 1
 EPI_NONE, EPI_RELU, EPI_GLU, EPI_RESIDUAL, EPI_RELU_BWD = 0, 1, 2, 3, 5
