@@ -615,6 +615,12 @@ int tnt_decoder_score_host(tnt_decoder* d, const int64_t* ids_host, const int64_
  * restores the full copy.)  tnt_decoder_last_h2d_bytes = bytes the last score_host / submit call actually copied. */
 uint64_t tnt_decoder_last_h2d_bytes(const tnt_decoder* d);
 
+/* The live-row copy on its own (for callers that prefetch their step inputs themselves): dst [S, B, E] device, src [S, B, E]
+ * pinned host, mask_host [B, S] bytes (nonzero = padding; NULL = plain copy).  Returns the bytes copied (< 0: tnt_status).
+ * Skipped rows of dst keep their previous contents: zero dst once. */
+int64_t tnt_h2d_live_rows(void* dst, const void* src_host, const uint8_t* mask_host, int S, int B, int E, int dtype,
+                          tnt_stream stream);
+
 /* Pipelined form of tnt_decoder_score_host with two slots: submit(slot) issues the H2D copies of that
  * batch on a private copy stream (overlapping the compute of the other slot), then forward + loss + the
  * D2H of (loss, n_tokens) on `stream`; wait(slot) blocks until out2_host of that slot is valid.

@@ -202,6 +202,7 @@ _SIGS = {
     'tnt_decoder_score_host_submit': (i32, [vp, i32, vp, vp, C.POINTER(Contexts), vp, vp, C.c_size_t, vp, C.c_size_t, vp]),
     'tnt_decoder_score_host_wait': (i32, [vp, i32]),
     'tnt_decoder_last_h2d_bytes': (C.c_uint64, [vp]),
+    'tnt_h2d_live_rows': (C.c_int64, [vp, vp, vp, i32, i32, i32, i32, vp]),
     'tnt_dropout_bits': (C.c_uint32, [C.c_uint64, C.c_uint32, C.c_uint64]),
     'tnt_dropout_apply': (i32, [vp, i64, vp, i64, vp, i64, i32, i32, i32, C.POINTER(Dropout), vp]),
     'tnt_decoder_set_dropout': (i32, [vp, C.POINTER(DropoutConfig)]),

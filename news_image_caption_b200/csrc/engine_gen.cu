@@ -454,6 +454,38 @@ extern "C" int tnt_decoder_score_host_submit(tnt_decoder* D, int slot, const int
   return TNT_OK;
 }
 
+// The live-row copy on its own, for callers that stage their step inputs themselves (a prefetching data loader: the
+// training / generation legs of bench.py): dst [S, B, E] device, src [S, B, E] PINNED host, mask [B, S] host bytes
+// (nonzero = padding) or NULL for a plain copy.  The skipped rows of dst are left as they are: zero dst once.
+extern "C" int64_t tnt_h2d_live_rows(void* dst, const void* src_host, const uint8_t* mask_host, int S, int B, int E, int dtype,
+                                     tnt_stream stream) {
+  using namespace tnt;
+  if (!dst || !src_host || S < 0 || B <= 0 || E <= 0) {
+    set_error("h2d_live_rows: bad arguments");
+    return TNT_ERR_ARG;
+  }
+  const size_t row = static_cast<size_t>(E) * dtype_size(dtype), pitch = static_cast<size_t>(B) * row;
+  cudaStream_t st = as_stream(stream);
+  int64_t bytes = 0;
+  if (!mask_host) {
+    if (cudaMemcpyAsync(dst, src_host, pitch * S, cudaMemcpyHostToDevice, st) != cudaSuccess) return TNT_ERR_CUDA;
+    return static_cast<int64_t>(pitch * S);
+  }
+  for (int b = 0; b < B; ++b) {
+    const uint8_t* m = mask_host + static_cast<size_t>(b) * S;
+    int len = S;
+    while (len > 0 && m[len - 1]) --len;
+    if (!len) continue;
+    if (cudaMemcpy2DAsync(static_cast<char*>(dst) + b * row, pitch, static_cast<const char*>(src_host) + b * row, pitch, row, len,
+                          cudaMemcpyHostToDevice, st) != cudaSuccess) {
+      set_error("h2d_live_rows: cudaMemcpy2DAsync failed");
+      return TNT_ERR_CUDA;
+    }
+    bytes += static_cast<int64_t>(row) * len;
+  }
+  return bytes;
+}
+
 // host -> device bytes the last tnt_decoder_score_host / _submit call copied (ids, targets, masks and the LIVE rows of every
 // memory source): what bench.py reports as e2e.h2d_bytes_per_step
 extern "C" uint64_t tnt_decoder_last_h2d_bytes(const tnt_decoder* D) { return D ? D->last_h2d_bytes : 0; }

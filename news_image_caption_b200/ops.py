@@ -444,3 +444,20 @@ def adam_step(params, grads, m, v, lr, step, betas=(0.9, 0.98), eps=1e-9, weight
     """torch.optim.Adam over flat fp32 arenas (tnt_adam_step): the final* scripts' optimizer (custom_v4.py:491)."""
     _lib.check(_lib.lib().tnt_adam_step(_p(params), _p(grads), _p(m), _p(v), params.numel(), None, float(grad_scale), float(lr),
                                         betas[0], betas[1], eps, weight_decay, int(step), _st()), 'tnt_adam_step')
+
+
+def h2d_live_rows(dst, src_host, mask_host=None):
+    """dst [S, B, E] (device) <- src_host [S, B, E] (pinned), only the rows s < len_b of every caption b when a host
+    key-padding mask [B, S] (True = padding) is given (tnt_h2d_live_rows); on the current stream.  Returns the bytes copied."""
+    S, B, E = src_host.shape
+    if not (src_host.is_pinned() and src_host.is_contiguous() and dst.is_contiguous() and dst.shape == src_host.shape):
+        raise ValueError('h2d_live_rows: contiguous pinned source and a device tensor of the same shape')
+    m = None
+    if mask_host is not None:
+        m = mask_host.contiguous()
+        if m.dtype != torch.bool or tuple(m.shape) != (B, S) or m.is_cuda:
+            raise ValueError('h2d_live_rows: mask must be a host bool tensor [B, S]')
+    n = _lib.lib().tnt_h2d_live_rows(_p(dst), _p(src_host), _p(m) if m is not None else None, S, B, E, _code(dst), _st())
+    if n < 0:
+        _lib.check(int(n), 'tnt_h2d_live_rows')
+    return int(n)
