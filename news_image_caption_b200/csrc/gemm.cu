@@ -324,6 +324,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           // pad rows of a dynamic-M problem get zeros: a later TN GEMM reduces over whole 64-row blocks
           zero_store<TOut, 32>(g, grp, row, n0);
         }
+        if (EPI == EPI_NONE && sizeof(TOut) == 4 && !g.vec_ok && !g.m_dyn) {
+          // unaligned fp32 rows: bias, then a register transpose so that the stores are coalesced (warp-collective)
+          float acc[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) acc[i] = (num_kb > 0 ? __uint_as_float(v[i]) : 0.f) * g.alpha;
+          if (g.bias) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[i] += sb[c * 32 + i];
+          }
+          store_block_transposed(g, grp, row - lane, M, n0, acc, lane);
+          return;
+        }
         if (row < M) {
           float acc[32];
 #pragma unroll

@@ -151,6 +151,39 @@ __device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m
   }
 }
 
+// In-register 32 x 32 transpose across a warp: before, lane l holds v[j] = element (row l, column j); after, lane l holds
+// v[j] = element (row j, column l).  Five butterfly stages of 16 exchanges (static register indices only).
+__device__ __forceinline__ void warp_transpose32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int k = 16; k >= 1; k >>= 1) {
+    const bool hi = (lane & k) != 0;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      if ((i & k) == 0) {
+        const float send = hi ? v[i] : v[i + k];
+        const float recv = __shfl_xor_sync(0xffffffffu, send, k);
+        if (hi) v[i] = recv;
+        else v[i + k] = recv;
+      }
+    }
+  }
+}
+
+// fp32 output whose leading dimension allows no 16-byte stores (the [rows, 50265] log-probability matrix of
+// AdaptiveSoftmax.get_log_prob): one thread per row writing 32 scalars put 32 partial sectors on the bus per store
+// instruction (196 TFLOP/s for the M = 2048, N = 30265 tail GEMM: store bound).  The warp's 32 x 32 block is transposed in
+// registers instead and written row by row: every store instruction covers 128 CONTIGUOUS bytes of one output row.
+// Warp-collective: every lane calls it (rows >= M and columns >= N are skipped inside).  row0 = row of lane 0.
+__device__ __forceinline__ void store_block_transposed(const GemmArgs& g, int grp, int row0, int M, int n0, float (&acc)[32], int lane) {
+  warp_transpose32(acc, lane);
+  float* c0 = reinterpret_cast<float*>(g.c) + grp * g.sc + static_cast<long>(row0) * g.ldc + n0 + lane;
+  if (n0 + lane < g.N) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (row0 + j < M) c0[static_cast<long>(j) * g.ldc] = acc[j];
+  }
+}
+
 // zeros into columns [n0, n0+NC) of output row m (pad rows of a dynamic-M problem)
 template <typename TOut, int NC>
 __device__ __forceinline__ void zero_store(const GemmArgs& g, int grp, int m, int n0) {
