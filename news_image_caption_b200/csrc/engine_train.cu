@@ -108,6 +108,8 @@ struct Ctx {
   cudaStream_t st;
   int dt;
   const tnt_dropout_config* dr;     // this step's dropout (seed already advanced) or NULL
+  cudaStream_t side = nullptr;      // side stream of the parameter-gradient tails (NULL: everything on `st`)
+  bool side_pending = false;        // work issued on `side` since the last join
   float* grad(const std::string& key) {
     auto it = D->grads.find(key);
     return it == D->grads.end() ? nullptr : it->second;
@@ -141,25 +143,49 @@ int ln_bwd(Ctx& c, const void* x, long ldx, const void* dy, long lddy, void* dx,
   return tnt_layernorm_bwd(&p, c.st);
 }
 
+// Side stream protocol.  side_fork: everything issued on `st` so far is visible to the work that follows on `side`.
+// side_join: `st` waits for the side work -- REQUIRED before `st` overwrites a buffer a side kernel reads (w.dW before
+// the next weight-gradient GEMM, a dY buffer before its next writer) and before a stage event is recorded.
+int side_fork(Ctx& c) {
+  if (!c.side) return TNT_OK;
+  TNT_CUDA(cudaEventRecord(c.D->side_fork, c.st));
+  TNT_CUDA(cudaStreamWaitEvent(c.side, c.D->side_fork, 0));
+  c.side_pending = true;
+  return TNT_OK;
+}
+int side_join(Ctx& c) {
+  if (!c.side || !c.side_pending) return TNT_OK;
+  TNT_CUDA(cudaEventRecord(c.D->side_join, c.side));
+  TNT_CUDA(cudaStreamWaitEvent(c.st, c.D->side_join, 0));
+  c.side_pending = false;
+  return TNT_OK;
+}
+inline cudaStream_t side_or_main(Ctx& c) { return c.side ? c.side : c.st; }
+
 // gradient of a GehringLinear: dWp [rows(prepared order), cols] fp32 -> weight_v / weight_g (or plain weight)
+// (side stream: the caller joins before dWp is overwritten)
 int linear_param_grads(Ctx& c, const std::string& prefix, const float* dWp, int rows, int cols, bool glu) {
   const float* g = c.raw(prefix + "weight_g");
   if (g) {
     const float* v = c.raw(prefix + "weight_v");
     float *dv = c.grad(prefix + "weight_v"), *dg = c.grad(prefix + "weight_g");
     TNT_CHECK_ARG(v && dv && dg, "train: '%sweight_v/_g' parameter or gradient buffer missing", prefix.c_str());
-    return wn_bwd(v, g, dWp, cols, dv, dg, rows, cols, glu, c.st);
+    TNT_TRY(side_fork(c));
+    return wn_bwd(v, g, dWp, cols, dv, dg, rows, cols, glu, side_or_main(c));
   }
   const float* v = c.raw(prefix + "weight");
   float* dv = c.grad(prefix + "weight");
   TNT_CHECK_ARG(v && dv, "train: '%sweight' parameter or gradient buffer missing", prefix.c_str());
-  return wn_bwd(v, nullptr, dWp, cols, dv, nullptr, rows, cols, glu, c.st);
+  TNT_TRY(side_fork(c));
+  return wn_bwd(v, nullptr, dWp, cols, dv, nullptr, rows, cols, glu, side_or_main(c));
 }
 
+// (side stream: the caller joins before dy is overwritten)
 int bias_grad(Ctx& c, const std::string& key, const void* dy, long ld, int M, int N, bool deinterleave, long offset = 0) {
   float* g = c.grad(key);
   TNT_CHECK_ARG(g, "train: gradient buffer for '%s' missing", key.c_str());
-  return colsum(dy, ld, M, N, nullptr, g + offset, c.dt, deinterleave, false, c.st);
+  TNT_TRY(side_fork(c));
+  return colsum(dy, ld, M, N, nullptr, g + offset, c.dt, deinterleave, false, side_or_main(c));
 }
 
 inline const char* off(const void* p, size_t elems, size_t E) { return static_cast<const char*>(p) + elems * E; }
@@ -238,11 +264,13 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
   TNT_TRY(linear_param_grads(c, p + "fc2.", w.dW, d, ffn, false));
   TNT_TRY(bias_grad(c, p + "fc2.bias", g_ffn, d, N, d, false));
   TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.dF, ffn, L.wf1, d, w.gC, d, N, d, ffn, dt, w.gB, d));      // gC = dX0
+  TNT_TRY(side_join(c));                          // w.dW is rewritten
   TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.dF, ffn, a.X0, d, w.dW, d, ffn, d, N, TNT_F32));
   TNT_TRY(linear_param_grads(c, p + "fc1.", w.dW, ffn, d, false));
   TNT_TRY(bias_grad(c, p + "fc1.bias", w.dF, ffn, N, ffn, false));
   // ---- context_fc over the concatenated, layer-normed per-source branches
   TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.gC, d, L.wc, nsd, w.dCAT, nsd, N, ns * d, d, dt));
+  TNT_TRY(side_join(c));                          // w.dW is rewritten
   TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.gC, d, a.CATln, nsd, w.dW, nsd, d, ns * d, N, TNT_F32));
   TNT_TRY(linear_param_grads(c, p + "context_fc.", w.dW, d, ns * d, false));
   TNT_TRY(bias_grad(c, p + "context_fc.bias", w.gC, d, N, d, false));
@@ -295,6 +323,7 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
     TNT_TRY(dropout_apply(w.gB, d, nullptr, 0, w.gA, d, N, d, dt, drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_CONV_OUT)), c.st));
     g_l2 = w.gA;
   }
+  TNT_TRY(side_join(c));                          // w.gC (read by the context_fc bias sum) and w.dW are rewritten
   TNT_TRY(gemm(c, TNT_NN, EPI_NONE, g_l2, d, L.w2, d, w.gC, d, N, d, d, dt));                         // gC = dcbuf
   TNT_TRY(gemm(c, TNT_TN, EPI_NONE, g_l2, d, a.cbuf, d, w.dW, d, d, d, N, TNT_F32));
   TNT_TRY(linear_param_grads(c, p + "linear2.", w.dW, d, d, false));
@@ -316,6 +345,7 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
   const void* X1in = in_drop ? a.Xd : Xin;        // what linear1 read in the forward
   TNT_TRY(gemm(c, TNT_NT, EPI_NONE, X1in, d, L.w1, d, w.raw, 2 * d, N, 2 * d, d, dt, nullptr, 0, nullptr, 0.f, L.b1));
   TNT_TRY(glu_bwd(w.raw, 2 * d, w.gC, d, w.draw, 2 * d, N, d, dt, c.st));
+  TNT_TRY(side_join(c));                          // w.gA (the masked linear2 gradient the bias sum reads) and w.dW are rewritten
   if (in_drop) {                                  // gA = dXin = drop(draw . W1) + dyc
     TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.draw, 2 * d, L.w1, d, w.gC, d, N, d, 2 * d, dt));
     TNT_TRY(dropout_apply(w.gC, d, w.gB, d, w.gA, d, N, d, dt, drop_site(dr, dr->input_dropout, TNT_DROP_SITE(l, TNT_DROP_INPUT)), c.st));
@@ -342,10 +372,13 @@ int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, int s) {
   const void* dkv = off(w.dkv[s], static_cast<size_t>(l) * 2 * d, E);     // columns [K | V] of this layer
   float *gk = c.grad(at + "bias_k"), *gv = c.grad(at + "bias_v"), *gb = c.grad(at + "in_proj_bias");
   TNT_CHECK_ARG(gk && gv && gb, "train: gradient buffer for '%sbias_k / bias_v / in_proj_bias' missing", at.c_str());
+  TNT_TRY(side_join(c));                          // w.dW is rewritten below
   TNT_TRY(kv_extra_grad(dkv, ldkv, S, B, 2 * d, w.vecs, c.dt, c.st));      // the learned extra key row (index S)
   TNT_CUDA(cudaMemcpyAsync(gk, w.vecs, sizeof(float) * d, cudaMemcpyDeviceToDevice, c.st));
   TNT_CUDA(cudaMemcpyAsync(gv, w.vecs + d, sizeof(float) * d, cudaMemcpyDeviceToDevice, c.st));
-  TNT_TRY(colsum(dkv, ldkv, S * B, 2 * d, nullptr, gb + d, c.dt, false, false, c.st));
+  // the bias column sum streams dkv from HBM beside the (tensor-bound) weight-gradient GEMM below
+  TNT_TRY(side_fork(c));
+  TNT_TRY(colsum(dkv, ldkv, S * B, 2 * d, nullptr, gb + d, c.dt, false, false, side_or_main(c)));
   float* gi = c.grad(at + "in_proj_weight");
   float* dst = gi ? gi + static_cast<size_t>(d) * d : w.dW;
   // A long reduction (the article: S*B = 32768 rows) over only (2d/128) x (kd/256) output tiles leaves most SMs idle, and
@@ -479,6 +512,14 @@ int step_setup(tnt_decoder* D, const tnt_contexts* ctx, void* workspace, size_t 
     set_error("%s: workspace %zu < %zu", who, workspace_bytes, s->w.total);
     return TNT_ERR_WORKSPACE;
   }
+  static const bool use_side = !(getenv("TNT_TRAIN_SIDE_STREAM") && atoi(getenv("TNT_TRAIN_SIDE_STREAM")) == 0);
+  if (use_side && !D->side_stream) {
+    int lo = 0, hi = 0;
+    TNT_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    TNT_CUDA(cudaStreamCreateWithPriority(&D->side_stream, cudaStreamNonBlocking, hi));
+    TNT_CUDA(cudaEventCreateWithFlags(&D->side_fork, cudaEventDisableTiming));
+    TNT_CUDA(cudaEventCreateWithFlags(&D->side_join, cudaEventDisableTiming));
+  }
   while (static_cast<int>(D->stage_events.size()) < Ls + 2) {
     cudaEvent_t e;
     TNT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -521,6 +562,7 @@ int train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, co
   const tnt_decoder_config& cf = D->cfg;
   const int B = ctx->B, T = ctx->T, N = B * T, d = cf.d, ns = cf.n_sources, Ls = cf.n_layers;
   Ctx c{D, st, cf.dtype, dr};
+  c.side = D->side_stream;
   if (!ext) TNT_TRY(adasoftmax_nll(D->ada, w.Xbt, d, target, N, cf.pad_idx, out2, w.loss_fwd, w.loss_fwd_bytes, st));
   // ---------------- backward: loss
   const int nt = cf.n_clusters - 1;
@@ -545,6 +587,7 @@ int train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, co
     const void* xin = l == 0 ? w.emb : w.act[l - 1].Xout;
     TNT_TRY(layer_bwd(c, ctx, w, l, xin, (ext && l == Ls - 1) ? ext->dattn : nullptr));
     for (int s = 0; s < ns; ++s) TNT_TRY(kv_param_grads(c, ctx, w, l, s));
+    TNT_TRY(side_join(c));
     TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], st));
   }
   const tnt_dropout d_emb = drop_site(dr, dr ? dr->dropout : 0.f, TNT_DROP_SITE_EMBED);
