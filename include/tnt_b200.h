@@ -198,11 +198,12 @@ typedef struct {
   const void* dy; int64_t lddy;
   void* dx; int64_t lddx;
   const float* gamma;
-  float* dgamma; float* dbeta;    /* [C] fp32, accumulated with atomics (must be zeroed) */
+  float* dgamma; float* dbeta;    /* [C] fp32, accumulated with atomics (must be zeroed, or set zero_param_grads) */
   int rows, C;
   float eps;
   int dtype;
   int variant;                    /* 0 = nn.LayerNorm; 1 = final* LayerNorm (unbiased std, eps outside), transformer_v2.py:82-94 */
+  int zero_param_grads;           /* 1: the call zeroes dgamma / dbeta itself (no separate memset launches) */
 } tnt_layernorm_bwd_params;
 int tnt_layernorm_bwd(const tnt_layernorm_bwd_params* p, tnt_stream stream);
 
@@ -587,8 +588,14 @@ typedef struct {
   const float* grad_scale_dev;     /* optional device scalar multiplied into the gradients (e.g. 1 / n_tokens) */
   float grad_scale;                /* host scalar, 0 means 1 */
   float max_grad_norm, lr, beta1, beta2, eps, weight_decay;
+  int norms_ready;                 /* 1: seg_sq already holds this step's per-tensor sums of squares (tnt_grad_sqnorm) */
 } tnt_adam_params;
 int tnt_bert_adam_step(const tnt_adam_params* p, tnt_stream stream);
+/* seg_sq[segment] += sum of squares of grads[first, first + n) (whole 64-element chunks): the norm pass of the step above,
+ * callable per arena slice as soon as that slice's gradients are final (the trainer runs it stage by stage on a side
+ * stream beside the backward pass; seg_sq must have been zeroed once per step). */
+int tnt_grad_sqnorm(const float* grads, const int* seg_of_chunk, float* seg_sq, int64_t first, int64_t n,
+                    tnt_stream stream);
 
 /* torch.optim.Adam over flat fp32 arenas -- the optimizer of the final* scripts: Adam(betas=(0.9, 0.98), eps=1e-9) driven by
  * the Noam schedule rate(step) = factor * d_model^-0.5 * min(step^-0.5, step * warmup^-1.5)

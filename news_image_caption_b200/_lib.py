@@ -82,7 +82,8 @@ class LayernormParams(C.Structure):
 
 class LayernormBwdParams(C.Structure):
     _fields_ = [('x', vp), ('ldx', i64), ('dy', vp), ('lddy', i64), ('dx', vp), ('lddx', i64), ('gamma', vp),
-                ('dgamma', vp), ('dbeta', vp), ('rows', i32), ('C', i32), ('eps', f32), ('dtype', i32), ('variant', i32)]
+                ('dgamma', vp), ('dbeta', vp), ('rows', i32), ('C', i32), ('eps', f32), ('dtype', i32), ('variant', i32),
+                ('zero_param_grads', i32)]
 
 
 class EmbedParams(C.Structure):
@@ -118,7 +119,7 @@ class XattnBwdParams(C.Structure):
 class AdamParams(C.Structure):
     _fields_ = [('params', vp), ('grads', vp), ('m', vp), ('v', vp), ('n', i64), ('seg_of_chunk', vp), ('seg_sq', vp),
                 ('n_segments', i32), ('grad_scale_dev', vp), ('grad_scale', f32), ('max_grad_norm', f32), ('lr', f32),
-                ('beta1', f32), ('beta2', f32), ('eps', f32), ('weight_decay', f32)]
+                ('beta1', f32), ('beta2', f32), ('eps', f32), ('weight_decay', f32), ('norms_ready', i32)]
 
 
 class LseParams(C.Structure):
@@ -158,6 +159,7 @@ _SIGS = {
     'tnt_dynconv_step': (i32, [C.POINTER(DynconvStepParams), vp]),
     'tnt_layernorm_fwd': (i32, [C.POINTER(LayernormParams), vp]),
     'tnt_layernorm_bwd': (i32, [C.POINTER(LayernormBwdParams), vp]),
+    'tnt_grad_sqnorm': (i32, [vp, vp, vp, i64, i64, vp]),
     'tnt_embed_fwd': (i32, [C.POINTER(EmbedParams), vp]),
     'tnt_context_mix': (i32, [C.POINTER(ContextMixParams), vp]),
     'tnt_nan_mask': (i32, [C.POINTER(NanMaskParams), vp]),

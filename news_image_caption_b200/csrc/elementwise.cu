@@ -227,6 +227,8 @@ __global__ void __launch_bounds__(128, 3) layernorm_bwd_cols_kernel(tnt_layernor
 #pragma unroll
   for (int j = 0; j < 8; ++j) g[j] = dg[j] = db[j] = 0.f;
   if (act) load8(p.gamma + tid * 8, g);
+  if (p.zero_param_grads && blockIdx.x == 0)     // the finish kernel (next launch in the stream) accumulates into them
+    for (int i = tid; i < p.C; i += 128) p.dgamma[i] = p.dbeta[i] = 0.f;
   const float invC = 1.f / p.C;
   auto fetch = [&](int row0, V (&xv)[R], V (&dv)[R]) {
 #pragma unroll
@@ -610,12 +612,18 @@ extern "C" int tnt_layernorm_bwd(const tnt_layernorm_bwd_params* p, tnt_stream s
   using namespace tnt;
   TNT_CHECK_ARG(p && p->x && p->dy && p->dx && p->gamma && p->dgamma && p->dbeta, "layernorm_bwd: null pointer");
   TNT_CHECK_ARG(p->C % 8 == 0 && p->C <= 6000, "layernorm_bwd: C");
+  const bool cols_shape = p->C <= 1024 && aligned16(p->x) && aligned16(p->dy) && aligned16(p->dx) && p->ldx % 8 == 0 &&
+                          p->lddy % 8 == 0 && p->lddx % 8 == 0 && (reinterpret_cast<uintptr_t>(p->gamma) & 15) == 0;
+  static const bool cols_on0 = [] { const char* e = getenv("TNT_LN_BWD_COLS"); return !(e && e[0] == '0'); }();
+  if (p->zero_param_grads && (p->rows == 0 || !(cols_on0 && cols_shape))) {      // only the column kernel zeroes in-kernel
+    TNT_CUDA(cudaMemsetAsync(p->dgamma, 0, sizeof(float) * p->C, as_stream(stream)));
+    TNT_CUDA(cudaMemsetAsync(p->dbeta, 0, sizeof(float) * p->C, as_stream(stream)));
+  }
   if (p->rows == 0) return TNT_OK;
   const int grid = std::min((p->rows + kWarps - 1) / kWarps, 2 * num_sms());
   const size_t smem = 2 * static_cast<size_t>(p->C) * 4;
   static const bool cols_on = [] { const char* e = getenv("TNT_LN_BWD_COLS"); return !(e && e[0] == '0'); }();
-  if (cols_on && p->C <= 1024 && aligned16(p->x) && aligned16(p->dy) && aligned16(p->dx) && p->ldx % 8 == 0 && p->lddy % 8 == 0 &&
-      p->lddx % 8 == 0 && (reinterpret_cast<uintptr_t>(p->gamma) & 15) == 0) {
+  if (cols_on && cols_shape) {
     const int R = 4;
     static const int per_sm_c = [] { const char* e = getenv("TNT_LN_BWD_COLS_CTAS_PER_SM"); return e ? std::max(1, atoi(e)) : 3; }();
     const int grid_c = std::min(std::min((p->rows + R - 1) / R, per_sm_c * num_sms()), kLnMaxCtas);

@@ -135,9 +135,8 @@ int gemm(Ctx& c, int layout, int epi, const void* A, long lda, const void* W, lo
 int ln_bwd(Ctx& c, const void* x, long ldx, const void* dy, long lddy, void* dx, long lddx, const float* gamma,
            float* dgamma, float* dbeta, int rows, int C) {
   TNT_CHECK_ARG(dgamma && dbeta, "train: LayerNorm gradient buffer missing");
-  TNT_CUDA(cudaMemsetAsync(dgamma, 0, sizeof(float) * C, c.st));
-  TNT_CUDA(cudaMemsetAsync(dbeta, 0, sizeof(float) * C, c.st));
   tnt_layernorm_bwd_params p = {};
+  p.zero_param_grads = 1;
   p.x = x; p.ldx = ldx; p.dy = dy; p.lddy = lddy; p.dx = dx; p.lddx = lddx; p.gamma = gamma; p.dgamma = dgamma;
   p.dbeta = dbeta; p.rows = rows; p.C = C; p.eps = 1e-5f; p.dtype = c.dt;
   return tnt_layernorm_bwd(&p, c.st);
@@ -372,13 +371,14 @@ int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, int s) {
   const void* dkv = off(w.dkv[s], static_cast<size_t>(l) * 2 * d, E);     // columns [K | V] of this layer
   float *gk = c.grad(at + "bias_k"), *gv = c.grad(at + "bias_v"), *gb = c.grad(at + "in_proj_bias");
   TNT_CHECK_ARG(gk && gv && gb, "train: gradient buffer for '%sbias_k / bias_v / in_proj_bias' missing", at.c_str());
-  TNT_TRY(side_join(c));                          // w.dW is rewritten below
-  TNT_TRY(kv_extra_grad(dkv, ldkv, S, B, 2 * d, w.vecs, c.dt, c.st));      // the learned extra key row (index S)
-  TNT_CUDA(cudaMemcpyAsync(gk, w.vecs, sizeof(float) * d, cudaMemcpyDeviceToDevice, c.st));
-  TNT_CUDA(cudaMemcpyAsync(gv, w.vecs + d, sizeof(float) * d, cudaMemcpyDeviceToDevice, c.st));
-  // the bias column sum streams dkv from HBM beside the (tensor-bound) weight-gradient GEMM below
+  TNT_TRY(side_join(c));                          // w.dW is rewritten below (and w.vecs by the side work of this call)
+  // the extra-row gradients and the bias column sum stream dkv from HBM beside the (tensor-bound) weight-gradient GEMM
   TNT_TRY(side_fork(c));
-  TNT_TRY(colsum(dkv, ldkv, S * B, 2 * d, nullptr, gb + d, c.dt, false, false, side_or_main(c)));
+  cudaStream_t ss = side_or_main(c);
+  TNT_TRY(kv_extra_grad(dkv, ldkv, S, B, 2 * d, w.vecs, c.dt, ss));        // the learned extra key row (index S)
+  TNT_CUDA(cudaMemcpyAsync(gk, w.vecs, sizeof(float) * d, cudaMemcpyDeviceToDevice, ss));
+  TNT_CUDA(cudaMemcpyAsync(gv, w.vecs + d, sizeof(float) * d, cudaMemcpyDeviceToDevice, ss));
+  TNT_TRY(colsum(dkv, ldkv, S * B, 2 * d, nullptr, gb + d, c.dt, false, false, ss));
   float* gi = c.grad(at + "in_proj_weight");
   float* dst = gi ? gi + static_cast<size_t>(d) * d : w.dW;
   // A long reduction (the article: S*B = 32768 rows) over only (2d/128) x (kd/256) output tiles leaves most SMs idle, and

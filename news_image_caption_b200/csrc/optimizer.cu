@@ -17,29 +17,49 @@ constexpr int kChunk = 64;      // arena segments are padded to 64 elements; one
 
 // sum of squares per segment (segment = one parameter tensor).  Every warp owns a CONTIGUOUS run of chunks and
 // flushes one atomicAdd per segment change, so a 150 M-element arena costs a few thousand atomics.
-__global__ void __launch_bounds__(256) seg_sqnorm_kernel(const float* g, long n_chunks, const int* seg_of_chunk, float* seg_sq) {
+__global__ void __launch_bounds__(256) seg_sqnorm_kernel(const float* g, long c_begin, long c_end, const int* seg_of_chunk,
+                                                         float* seg_sq) {
   const int lane = threadIdx.x & 31;
   const long warp = (blockIdx.x * 256L + threadIdx.x) >> 5;
   const long nw = (gridDim.x * 256L) >> 5;
-  const long per = (n_chunks + nw - 1) / nw;
-  const long c0 = warp * per, c1 = min(n_chunks, c0 + per);
+  const long per = (((c_end - c_begin) + nw - 1) / nw + 7) & ~7L;       // runs of 8 chunks: four 16-byte loads per lane
+  const long c0 = c_begin + warp * per, c1 = min(c_end, c0 + per);
   float acc = 0.f;
-  int cur = c0 < c1 ? seg_of_chunk[c0] : -1;
-  for (long c = c0; c < c1; ++c) {
-    const int sg = seg_of_chunk[c];
-    if (sg != cur) {
-      acc = warp_sum(acc);
-      if (lane == 0 && acc != 0.f) atomicAdd(seg_sq + cur, acc);
-      acc = 0.f;
-      cur = sg;
+  int cur = -1;
+  auto flush = [&](int next) {
+    acc = warp_sum(acc);
+    if (lane == 0 && cur >= 0 && acc != 0.f) atomicAdd(seg_sq + cur, acc);
+    acc = 0.f;
+    cur = next;
+  };
+  long c = c0;
+  for (; c + 8 <= c1; c += 8) {
+    const int sid = seg_of_chunk[c + (lane & 7)];
+    const int first = __shfl_sync(0xffffffffu, sid, 0);
+    if (__all_sync(0xffffffffu, sid == first)) {
+      if (first != cur) flush(first);
+      const float4* p = reinterpret_cast<const float4*>(g + c * kChunk);
+      const float4 v0 = p[lane], v1 = p[lane + 32], v2 = p[lane + 64], v3 = p[lane + 96];
+      acc = fmaf(v0.x, v0.x, fmaf(v0.y, v0.y, fmaf(v0.z, v0.z, fmaf(v0.w, v0.w, acc))));
+      acc = fmaf(v1.x, v1.x, fmaf(v1.y, v1.y, fmaf(v1.z, v1.z, fmaf(v1.w, v1.w, acc))));
+      acc = fmaf(v2.x, v2.x, fmaf(v2.y, v2.y, fmaf(v2.z, v2.z, fmaf(v2.w, v2.w, acc))));
+      acc = fmaf(v3.x, v3.x, fmaf(v3.y, v3.y, fmaf(v3.z, v3.z, fmaf(v3.w, v3.w, acc))));
+    } else {                                     // a tensor boundary inside the run: chunk by chunk
+      for (int j = 0; j < 8; ++j) {
+        const int sg = __shfl_sync(0xffffffffu, sid, j);
+        if (sg != cur) flush(sg);
+        const float2 v = *reinterpret_cast<const float2*>(g + (c + j) * kChunk + lane * 2);
+        acc = fmaf(v.x, v.x, fmaf(v.y, v.y, acc));
+      }
     }
+  }
+  for (; c < c1; ++c) {
+    const int sg = seg_of_chunk[c];
+    if (sg != cur) flush(sg);
     const float2 v = *reinterpret_cast<const float2*>(g + c * kChunk + lane * 2);
     acc = fmaf(v.x, v.x, fmaf(v.y, v.y, acc));
   }
-  if (cur >= 0) {
-    acc = warp_sum(acc);
-    if (lane == 0 && acc != 0.f) atomicAdd(seg_sq + cur, acc);
-  }
+  flush(-1);
 }
 
 __global__ void __launch_bounds__(256) bert_adam_kernel(float* p, const float* g, float* m, float* v, long n_chunks,
@@ -87,14 +107,27 @@ extern "C" int tnt_bert_adam_step(const tnt_adam_params* a, tnt_stream stream) {
   cudaStream_t st = as_stream(stream);
   const long n_chunks = a->n / kChunk;
   const int grid = static_cast<int>(std::min<long>((a->n / 4 + 255) / 256, 16L * num_sms()));
-  if (a->max_grad_norm > 0.f) {
+  if (a->max_grad_norm > 0.f && !a->norms_ready) {
     TNT_CUDA(cudaMemsetAsync(a->seg_sq, 0, sizeof(float) * a->n_segments, st));
-    seg_sqnorm_kernel<<<grid, 256, 0, st>>>(a->grads, n_chunks, a->seg_of_chunk, a->seg_sq);
+    seg_sqnorm_kernel<<<grid, 256, 0, st>>>(a->grads, 0, n_chunks, a->seg_of_chunk, a->seg_sq);
     TNT_LAUNCHED();
   }
   bert_adam_kernel<<<grid, 256, 0, st>>>(a->params, a->grads, a->m, a->v, n_chunks, a->seg_of_chunk, a->seg_sq,
                                          a->grad_scale_dev, a->grad_scale != 0.f ? a->grad_scale : 1.f, a->max_grad_norm,
                                          a->lr, a->beta1, a->beta2, a->eps, a->weight_decay);
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
+extern "C" int tnt_grad_sqnorm(const float* grads, const int* seg_of_chunk, float* seg_sq, int64_t first, int64_t n,
+                               tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(grads && seg_of_chunk && seg_sq && first >= 0 && n >= 0, "grad_sqnorm: bad arguments");
+  TNT_CHECK_ARG(first % kChunk == 0 && n % kChunk == 0, "grad_sqnorm: the range must be whole 64-element chunks");
+  TNT_CHECK_ALIGN(aligned16(grads), "grad_sqnorm: alignment");
+  if (n == 0) return TNT_OK;
+  const int grid = static_cast<int>(std::min<long>((n / 4 + 255) / 256, 16L * num_sms()));
+  seg_sqnorm_kernel<<<grid, 256, 0, as_stream(stream)>>>(grads, first / kChunk, (first + n) / kChunk, seg_of_chunk, seg_sq);
   TNT_LAUNCHED();
   return TNT_OK;
 }

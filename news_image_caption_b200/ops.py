@@ -171,9 +171,10 @@ def layernorm_bwd(x, dy, gamma, eps=1e-5, variant=0):
     Cc = x.shape[-1]
     dx = torch.empty_like(x)
     gamma = gamma.float().contiguous()
-    dg = torch.zeros(Cc, dtype=torch.float32, device=x.device)
-    db = torch.zeros(Cc, dtype=torch.float32, device=x.device)
+    dg = torch.full((Cc,), 7.0, dtype=torch.float32, device=x.device)      # stale contents: the call zeroes them itself
+    db = torch.full((Cc,), 7.0, dtype=torch.float32, device=x.device)
     p = _lib.LayernormBwdParams()
+    p.zero_param_grads = 1
     p.x, p.ldx, p.dy, p.lddy, p.dx, p.lddx = x.data_ptr(), Cc, dy.data_ptr(), Cc, dx.data_ptr(), Cc
     p.gamma, p.dgamma, p.dbeta = gamma.data_ptr(), dg.data_ptr(), db.data_ptr()
     p.rows, p.C, p.eps, p.dtype, p.variant = x.numel() // Cc, Cc, eps, _code(x), variant

@@ -170,6 +170,14 @@ class Trainer:
         if self.exchange.world > 1 and __import__('os').environ.get('TNT_COMPUTE_PRIORITY', '1') != '0':
             self.compute_stream = torch.cuda.Stream(priority=-1)
         self.gscale = torch.ones(1, dtype=torch.float32, device='cuda')
+        # the per-tensor gradient norms BertAdam clips by can be summed slice by slice as soon as a stage's gradients are
+        # final (tnt_grad_sqnorm): data-parallel on the communication stream right after the slice's cast-back, so only the
+        # slices that are final last stay in the step's tail.  On ONE GPU (side stream beside the backward pass) it measured
+        # slightly slower than the single pass before BertAdam (7.61 vs 7.58 ms: the 0.1 ms HBM pass competes with the
+        # backward and costs two stream hops per stage), so it is off there unless TNT_STAGE_NORMS=1
+        env = __import__('os').environ.get('TNT_STAGE_NORMS')
+        self.stage_norms = max_grad_norm > 0 and (env == '1' or (env is None and self.exchange.world > 1))
+        self.norm_stream = torch.cuda.Stream() if (self.stage_norms and self.exchange.world == 1) else None
         # multi-GPU: the embedding rows of the tied band tables travel as a packed list (the arena keeps the band tables in
         # stage 0, where their dense softmax part is final); a band whose dim differs from d keeps the dense path
         self.sparse = None
@@ -216,17 +224,35 @@ class Trainer:
         dec, L = self.dec, _lib.lib()
         ids = prev_target['roberta'] if isinstance(prev_target, dict) else prev_target
         self._ensure_sparse(ids.shape[0] * ids.shape[1])
-        out = dec.train_step(prev_target, target, contexts, loss_scale=1.0)
         cur = torch.cuda.current_stream()
+        stage_norms = self.stage_norms and (self.exchange.world == 1 or self.overlap)
+        if stage_norms:
+            self.seg_sq.zero_()                 # on the step's stream: after the previous step's BertAdam read it
+        out = dec.train_step(prev_target, target, contexts, loss_scale=1.0)
+        h = dec._h()
+        n_stages = L.tnt_decoder_train_stages(h)
+        if not self.sparse_embed and dec.band_tables_in_stage0:
+            # dense embedding scatter: the band tables (arena stage 0) are only final when the backward ends
+            order = list(range(1, n_stages)) + [0]
+            wait_on = {0: n_stages - 1}
+        else:
+            order, wait_on = list(range(n_stages)), {}
+        late = []                               # slices whose norms can only be summed on the step's stream, at the end
+
+        def sqnorm(s, stream):
+            a, b = self.exchange.slices[s]
+            if a is not None and b > a:
+                _lib.check(L.tnt_grad_sqnorm(C.c_void_p(dec.flat_grads.data_ptr()), C.c_void_p(self.seg_of_chunk.data_ptr()),
+                                             C.c_void_p(self.seg_sq.data_ptr()), a, b - a, C.c_void_p(stream.cuda_stream)),
+                           'tnt_grad_sqnorm')
+        if self.exchange.world == 1 and stage_norms:
+            ns = self.norm_stream
+            for s in order:                     # the stage events order this after seg_sq.zero_() too
+                _lib.check(L.tnt_decoder_stream_wait_stage(h, wait_on.get(s, s), C.c_void_p(ns.cuda_stream)),
+                           'tnt_decoder_stream_wait_stage')
+                sqnorm(s, ns)
+            cur.wait_stream(ns)
         if self.exchange.world > 1:
-            h = dec._h()
-            n_stages = L.tnt_decoder_train_stages(h)
-            if not self.sparse_embed and dec.band_tables_in_stage0:
-                # dense embedding scatter: the band tables (arena stage 0) are only final when the backward ends
-                order = list(range(1, n_stages)) + [0]
-                wait_on = {0: n_stages - 1}
-            else:
-                order, wait_on = list(range(n_stages)), {}
             if self.overlap:
                 with torch.cuda.stream(self.comm_stream):
                     for j, s in enumerate(order):
@@ -235,6 +261,11 @@ class Trainer:
                         if j == 0:      # (loss_sum, n_tokens) exist once the forward has ended: exchanged here, off the step's tail
                             self.exchange.reduce_scalars(out)
                         self.exchange.reduce_slice(s)
+                        if stage_norms:
+                            if s == 0 and self.sparse is not None:
+                                late.append(s)          # the band tables still get the gathered embedding rows
+                            else:
+                                sqnorm(s, self.comm_stream)
                     if self.sparse is not None:
                         self.sparse.gather()
                     self.exchange.finish()
@@ -247,6 +278,8 @@ class Trainer:
                     self.sparse.gather()
             if self.sparse is not None:
                 self.sparse.scatter_into(dec.band_table_grads(), dec.embed_padding_idx)
+            for s in late:
+                sqnorm(s, cur)
         # gradient of the reference loss (sum-NLL / n_tokens / ln 2): scale by the global token count on the device
         # (an all-padding global batch has n_tokens == 0: every gradient is 0 then, keep the scale finite)
         torch.reciprocal(out[1:2].clamp_min(1.0) * math.log(2.0), out=self.gscale)
@@ -257,6 +290,7 @@ class Trainer:
         a.grad_scale_dev, a.grad_scale = self.gscale.data_ptr(), 1.0
         a.max_grad_norm, a.lr = self.max_norm, self.lr_now()
         a.beta1, a.beta2, a.eps, a.weight_decay = self.betas[0], self.betas[1], self.eps, self.wd
+        a.norms_ready = 1 if stage_norms else 0
         _lib.check(L.tnt_bert_adam_step(C.byref(a), C.c_void_p(cur.cuda_stream)), 'tnt_bert_adam_step')
         self.step_no += 1
         dec.mark_updated()
