@@ -246,6 +246,8 @@ class Trainer:
                                              C.c_void_p(self.seg_sq.data_ptr()), a, b - a, C.c_void_p(stream.cuda_stream)),
                            'tnt_grad_sqnorm')
         if self.exchange.world == 1 and stage_norms:
+            if self.norm_stream is None:
+                self.norm_stream = torch.cuda.Stream()
             ns = self.norm_stream
             for s in order:                     # the stage events order this after seg_sq.zero_() too
                 _lib.check(L.tnt_decoder_stream_wait_stage(h, wait_on.get(s, s), C.c_void_p(ns.cuda_stream)),
