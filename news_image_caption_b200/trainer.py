@@ -86,7 +86,7 @@ class GradientExchange:
             return
         w = dist.all_reduce(self.flat[a:b], op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
         if async_op:
-            self.pending.append((w, None, None))
+            w.wait()                    # stream-side: what follows on the calling stream (the slice's norm pass) sees the sum
 
     def reduce_scalars(self, t):
         if self.world > 1:
