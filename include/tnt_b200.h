@@ -340,6 +340,16 @@ typedef struct {
 } tnt_lse_params;
 size_t tnt_lse_workspace_bytes(int M, int n_cols, int dtype);
 int tnt_lse_fwd(const tnt_lse_params* p, tnt_stream stream);
+/* tnt_lse_fwd without a caller workspace.  No counterpart in the reference: added for
+ * callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same inputs, outputs and results as tnt_lse_fwd; p->workspace / workspace_bytes are ignored -- the partial statistics go
+ * to an 8 MiB device array built into the library (held by every GPU that loads it until exit), and the call performs no
+ * cudaMalloc / cudaFree or any other allocation.  Limit: M * ceil(n_cols / 32) * 16 bytes <= tnt_lse_fwd_static_max_bytes()
+ * (e.g. 256 rows over the 50265-word vocabulary, the decode-step size); larger problems return TNT_ERR_ARG with a message
+ * and must use tnt_lse_fwd.  All calls on a GPU share the array: calls that overlap on the GPU (different streams) race;
+ * calls ordered on one stream are safe, and nothing needs clearing between them. */
+size_t tnt_lse_fwd_static_max_bytes(void);
+int tnt_lse_fwd_static(const tnt_lse_params* p, tnt_stream stream);
 
 /* Backward of Generator + CrossEntropyLoss(ignore_index = pad, reduction = 'sum') of the final* scripts
  * (final_roberta2/transformer_v2.py:54-62, custom_v4.py:404-419, 489): from the row statistics tnt_lse_fwd wrote,

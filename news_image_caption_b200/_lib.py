@@ -159,6 +159,8 @@ _SIGS = {
     'tnt_dynconv_step': (i32, [C.POINTER(DynconvStepParams), vp]),
     'tnt_layernorm_fwd': (i32, [C.POINTER(LayernormParams), vp]),
     'tnt_layernorm_bwd': (i32, [C.POINTER(LayernormBwdParams), vp]),
+    'tnt_lse_fwd_static': (i32, [C.POINTER(LseParams), vp]),
+    'tnt_lse_fwd_static_max_bytes': (C.c_size_t, []),
     'tnt_grad_sqnorm': (i32, [vp, vp, vp, i64, i64, vp]),
     'tnt_embed_fwd': (i32, [C.POINTER(EmbedParams), vp]),
     'tnt_context_mix': (i32, [C.POINTER(ContextMixParams), vp]),

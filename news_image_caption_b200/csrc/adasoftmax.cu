@@ -575,3 +575,40 @@ extern "C" int tnt_lse_fwd(const tnt_lse_params* p, tnt_stream stream) {
                   p->n_cols, nullptr, 0, static_cast<float4*>(p->workspace), reinterpret_cast<float4*>(p->stats),
                   as_stream(stream));
 }
+
+// ------------------------------------------------------------------------------ tnt_lse_fwd without a caller workspace
+// The per-(row, column-tile) partial statistics live in a file-scope device array instead of a caller buffer, so the call
+// allocates nothing and needs no workspace query: for callers that cannot allocate (CUDA graph capture, serving loops).
+// Every GPU that loads the library holds the array until exit.  All calls share it: two calls that overlap on the GPU
+// (different streams) race.  Nothing in it has to start at zero -- the GEMM epilogue writes every entry the finish kernel
+// reads -- so the last call's contents are simply overwritten.
+namespace {
+constexpr size_t kLseStaticBytes = size_t(8) << 20;       // 8 MiB: M * ceil(n_cols / 32) <= 524288 partial records
+static __device__ __align__(256) unsigned char g_lse_static_scratch[kLseStaticBytes];
+}  // namespace
+
+extern "C" size_t tnt_lse_fwd_static_max_bytes(void) { return kLseStaticBytes; }
+
+extern "C" int tnt_lse_fwd_static(const tnt_lse_params* p, tnt_stream stream) {
+  using namespace tnt;
+  TNT_CHECK_ARG(p && p->x && p->w && p->stats, "lse_static: null pointer");
+  TNT_CHECK_ARG(p->M >= 0 && p->n_cols > 0 && p->K > 0, "lse_static: bad shape");
+  const size_t need = lse_partials_bytes(p->M, p->n_cols);
+  TNT_CHECK_ARG(need <= kLseStaticBytes,
+                "lse_static: M=%d x n_cols=%d needs %zu bytes of scratch, the built-in array holds %zu (M * ceil(n_cols / 32) <= %zu); "
+                "use tnt_lse_fwd with a caller workspace",
+                p->M, p->n_cols, need, kLseStaticBytes, kLseStaticBytes / sizeof(float4));
+  // in host code the array's name is a host-side stand-in: the device address comes from the runtime, once per device,
+  // with that device current
+  static float4* base[kMaxDevices] = {};
+  const int dev = cur_device();
+  if (!base[dev]) {
+    void* sp = nullptr;
+    TNT_CUDA(cudaGetSymbolAddress(&sp, g_lse_static_scratch));
+    TNT_CHECK_ARG(sp, "lse_static: no device address for the scratch array");
+    base[dev] = static_cast<float4*>(sp);
+  }
+  if (p->M == 0) return TNT_OK;
+  return lse_gemm(p->x, p->ldx, p->w, p->ldw, p->bias, p->M, p->n_cols, p->K, p->dtype, p->m_dyn, p->target, p->row_map,
+                  p->n_cols, nullptr, 0, base[dev], reinterpret_cast<float4*>(p->stats), as_stream(stream));
+}
