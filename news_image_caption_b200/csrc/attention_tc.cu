@@ -94,6 +94,12 @@ __device__ __forceinline__ float redux_max(float v) {
   asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
   return r;
 }
+// 2^x for x <= 0 (a probability relative to the column maximum): one MUFU instruction, results below 2^-126 flush to 0
+__device__ __forceinline__ float ex2_fast(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
 __device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
 // DROP: dropout on the probabilities, compiled in only for the training step (zero cost for inference).
@@ -260,6 +266,28 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     float* red_sum = red + 256 + (hd * 4 + quad) * 32;
     int ps = 0;
     uint32_t pph = 0, it = 0;
+    // key-padding bytes of this lane's key in every live tile of an item (head pairs): fetched one item AHEAD, behind the
+    // previous item's pass 2, so the global-load latency is not part of the softmax warps' serial chain (15 % of their
+    // stall samples when the bytes were loaded at the top of the item)
+    uint32_t mb[MAX_TILES];
+    auto fetch_mask = [&](int item_n) {
+      if (D128) return;
+#pragma unroll
+      for (int j = 0; j < MAX_TILES; ++j) mb[j] = 0;
+      if (!a.mask || item_n >= a.n_items) return;
+      const uint32_t ent_n = slot_entry(wl, listed, (item_n / a.n_qt) / HP, a.n_tiles);
+      const uint8_t* mrow = a.mask + static_cast<long>(ent_n & 0xFFFF) * a.m_stride_b;
+      uint32_t m = ent_n >> 16;
+#pragma unroll
+      for (int j = 0; j < MAX_TILES; ++j) {
+        if (m) {
+          const int key = (__ffs(m) - 1) * TKEYS + quad * 32 + lane;
+          if (key < a.S && key < a.mask_S) mb[j] = mrow[key];
+          m &= m - 1;
+        }
+      }
+    };
+    fetch_mask(blockIdx.x);
     for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
       const uint32_t par = it & 1;
       const int qt = item % a.n_qt, r = item / a.n_qt, hp = r % HP;
@@ -271,7 +299,17 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const bool score_warp = !D128 || hd == 0;      // D128: the second group of four warps has no score columns
       uint32_t valid = 0;             // bit j: this lane's key of the j-th LIVE tile takes part (D128: lies inside [0, S))
       uint32_t vis[D128 ? MAX_TILES : 1];            // D128: bit c of vis[j] = query c of this tile SEES the key (mask != 0)
-      {
+      if (!D128) {
+        uint32_t m = live;
+#pragma unroll
+        for (int j = 0; j < MAX_TILES; ++j) {
+          if (m) {
+            const int key = (__ffs(m) - 1) * TKEYS + quad * 32 + lane;
+            valid |= static_cast<uint32_t>(key < a.S && mb[j] == 0) << j;
+            m &= m - 1;
+          }
+        }
+      } else {
         int j = 0;
         for (uint32_t m = live; m; m &= m - 1, ++j) {
           const int key = (__ffs(m) - 1) * TKEYS + quad * 32 + lane;
@@ -291,8 +329,6 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
               }
             }
             vis[j] = w;
-          } else if (ok && a.mask && key < a.mask_S) {
-            ok = a.mask[static_cast<long>(b) * a.m_stride_b + key] == 0;
           }
           valid |= static_cast<uint32_t>(ok) << j;
         }
@@ -357,8 +393,8 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         uint32_t pk[16];
 #pragma unroll
         for (int c = 0; c < 32; c += 2) {
-          float p0 = ok ? exp2f(fmaf(__uint_as_float(v[c]), a.scale_log2e, -mx[c])) : 0.f;
-          float p1 = ok ? exp2f(fmaf(__uint_as_float(v[c + 1]), a.scale_log2e, -mx[c + 1])) : 0.f;
+          float p0 = ok ? ex2_fast(fmaf(__uint_as_float(v[c]), a.scale_log2e, -mx[c])) : 0.f;
+          float p1 = ok ? ex2_fast(fmaf(__uint_as_float(v[c + 1]), a.scale_log2e, -mx[c + 1])) : 0.f;
           ls[c] += p0;
           ls[c + 1] += p1;
           if (DROP) {
@@ -385,6 +421,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       ptx::tc_fence_before();
       __syncwarp();
       if (!a.weights && lane == 0) ptx::mbar_arrive(&bar->s_empty);        // score columns may be overwritten
+      fetch_mask(item + gridDim.x);      // the next item's mask bytes: in flight through the column sums and the epilogue
       // column sums across the warp, then across the 4 quadrant warps of this head
       float mysum = 0.f;
 #pragma unroll
@@ -414,7 +451,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
           for (int c = 0; c < 32; ++c) {
             const float inv = __shfl_sync(0xffffffffu, my_inv, c);
-            float pw = exp2f(fmaf(__uint_as_float(v[c]), a.scale_log2e, -mx[c]));
+            float pw = ex2_fast(fmaf(__uint_as_float(v[c]), a.scale_log2e, -mx[c]));
             if (DROP) {
               const unsigned long long i0 =
                   ((static_cast<unsigned long long>(b) * a.H + hp * 2 + hd) * a.T + qt * TQ + c) * a.S + tile * TKEYS + quad * 32 + lane;
@@ -437,6 +474,15 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       // ---- epilogue: O^T rows of this quadrant belong to head (quad / 2); this warp takes 16 queries
       const int oh = D128 ? 0 : quad >> 1;
       const int q0 = hd * 16;
+      // 1 / l of query q0 + (lane & 15), handed out below with one shuffle per query (a division and four shared-memory
+      // loads per ELEMENT made the epilogue a quarter of the kernel's instructions)
+      float inv_mine;
+      {
+        const float* rs = red + 256 + oh * 128;
+        const int q = q0 + (lane & 15);
+        const float l = rs[q] + rs[32 + q] + rs[64 + q] + rs[96 + q];
+        inv_mine = l > 0.f ? 1.f / l : 0.f;
+      }
       ptx::mbar_wait(&bar->o_ready, par);
       ptx::tc_fence_after();
       uint32_t o[16];
@@ -445,14 +491,15 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&bar->o_empty);
-      const float* rs = red + 256 + oh * 128;
       const int dch = D128 ? quad * 32 + lane : (quad & 1) * 32 + lane;      // channel inside the head
-      bf16* out = reinterpret_cast<bf16*>(a.out) + static_cast<long>(b) * a.o_stride_b + (D128 ? hp * 2 * D : (hp * 2 + oh) * D) + dch;
+      bf16* out = reinterpret_cast<bf16*>(a.out) + static_cast<long>(b) * a.o_stride_b + (D128 ? hp * 2 * D : (hp * 2 + oh) * D) + dch +
+                  static_cast<long>(qt * TQ + q0) * a.o_stride_t;
+      const int n_q = a.T - (qt * TQ + q0);                                  // queries of this block that exist
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
-        const int q = q0 + j, t = qt * TQ + q;
-        const float l = rs[q] + rs[32 + q] + rs[64 + q] + rs[96 + q];
-        if (t < a.T) out[static_cast<long>(t) * a.o_stride_t] = __float2bfloat16_rn(l > 0.f ? __uint_as_float(o[j]) / l : 0.f);
+        const float inv = __shfl_sync(0xffffffffu, inv_mine, j);
+        if (j < n_q) *out = __float2bfloat16_rn(__uint_as_float(o[j]) * inv);
+        out += a.o_stride_t;
       }
       named_bar(3, 256);                 // red[] is rewritten by the next item only after everyone has read it
     }
