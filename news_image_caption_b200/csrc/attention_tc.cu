@@ -392,9 +392,12 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
         uint32_t pk[16];
 #pragma unroll
+        for (int c = 0; c < 16; ++c) pk[c] = 0u;
+        if (ok)                                    // (a key outside the row contributes nothing: only a ragged tile diverges)
+#pragma unroll
         for (int c = 0; c < 32; c += 2) {
-          float p0 = ok ? ex2_fast(fmaf(__uint_as_float(v[c]), a.scale_log2e, -mx[c])) : 0.f;
-          float p1 = ok ? ex2_fast(fmaf(__uint_as_float(v[c + 1]), a.scale_log2e, -mx[c + 1])) : 0.f;
+          float p0 = ex2_fast(fmaf(__uint_as_float(v[c]), a.scale_log2e, -mx[c]));
+          float p1 = ex2_fast(fmaf(__uint_as_float(v[c + 1]), a.scale_log2e, -mx[c + 1]));
           ls[c] += p0;
           ls[c + 1] += p1;
           if (DROP) {
@@ -423,13 +426,19 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       if (!a.weights && lane == 0) ptx::mbar_arrive(&bar->s_empty);        // score columns may be overwritten
       fetch_mask(item + gridDim.x);      // the next item's mask bytes: in flight through the column sums and the epilogue
       // column sums across the warp, then across the 4 quadrant warps of this head
-      float mysum = 0.f;
+      // butterfly reduce-scatter: at distance ofs a lane keeps the half of its columns that its own bit selects and hands the
+      // other half to its partner -- 31 shuffles for the 32 sums (a full warp_sum per column: 160); lane L ends with column L
 #pragma unroll
-      for (int c = 0; c < 32; ++c) {
-        const float w = warp_sum(ls[c]);
-        if (lane == c) mysum = w;
+      for (int ofs = 16; ofs >= 1; ofs >>= 1) {
+        const bool up = (lane & ofs) != 0;
+#pragma unroll
+        for (int i = 0; i < ofs; ++i) {
+          const float send = up ? ls[i] : ls[i + ofs];
+          const float keep = up ? ls[i + ofs] : ls[i];
+          ls[i] = keep + __shfl_xor_sync(0xffffffffu, send, ofs);
+        }
       }
-      red_sum[lane] = mysum;
+      red_sum[lane] = ls[0];
       named_bar(3, 256);                 // the epilogue reads the sums of BOTH head groups
       if (a.weights) {
         // ---- pass 3 (last decoder layer only): head-averaged attention weights.  The scores are still resident in TMEM
