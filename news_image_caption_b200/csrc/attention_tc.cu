@@ -42,6 +42,7 @@ struct Args {
   int B, T, S, H, mask_S;
   float scale_log2e;
   int n_items, n_qt, n_tiles;
+  uint32_t mul_qt, mul_hp;                        // floor(2^32 / d) + 1 for d = n_qt, head slots: item -> (slot, hp, qt) without IDIV
   DropSpec drop;                                  // dropout on the probabilities (the normaliser stays un-dropped)
   const uint32_t* tile_live;                      // optional [B]: bit i set = key tile i of batch row b holds an un-masked key
   float* weights;                                 // optional [B, T, S] fp32, ZEROED by the launcher: head-averaged probabilities
@@ -81,6 +82,18 @@ __device__ __forceinline__ void build_work_list(const uint32_t* tile_live, int B
 // entry of batch slot bi: from the sorted list, or (bi, every tile) when there is none
 __device__ __forceinline__ uint32_t slot_entry(const uint32_t* wl, bool listed, int bi, int n_tiles) {
   return listed ? wl[bi] : (static_cast<uint32_t>(bi) | (((1u << n_tiles) - 1u) << 16));
+}
+
+// x / d for x * d < 2^32 (checked by the launcher) with mul = floor(2^32 / d) + 1; d == 1 has no 32-bit multiplier
+__device__ __forceinline__ int fast_div(int x, int d, uint32_t mul) { return d == 1 ? x : static_cast<int>(__umulhi(static_cast<uint32_t>(x), mul)); }
+struct ItemPos { int qt, hp, slot; };
+__device__ __forceinline__ ItemPos item_pos(int item, int n_qt, uint32_t mul_qt, int HP, uint32_t mul_hp) {
+  ItemPos p;
+  const int r = fast_div(item, n_qt, mul_qt);
+  p.qt = item - r * n_qt;
+  p.slot = fast_div(r, HP, mul_hp);
+  p.hp = r - p.slot * HP;
+  return p;
 }
 
 struct Bars {
@@ -170,8 +183,9 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       int ks = 0, vs = 0;
       uint32_t kph = 0, vph = 0, it = 0;
       for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
-        const int qt = item % a.n_qt, r = item / a.n_qt, hp = r % HP;
-        const uint32_t ent = slot_entry(wl, listed, r / HP, a.n_tiles);
+        const ItemPos ip = item_pos(item, a.n_qt, a.mul_qt, HP, a.mul_hp);
+        const int qt = ip.qt, hp = ip.hp;
+        const uint32_t ent = slot_entry(wl, listed, ip.slot, a.n_tiles);
         const int b = ent & 0xFFFF;
         const uint32_t live = ent >> 16;
         const int c0 = hp * 2 * D;
@@ -209,7 +223,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       uint32_t kph = 0, vph = 0, pph = 0, it = 0;
       for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
         const uint32_t par = it & 1;
-        const int nl = __popc(slot_entry(wl, listed, (item / a.n_qt) / HP, a.n_tiles) >> 16);   // live key tiles: score tile j at TMEM column j*64
+        const int nl = __popc(slot_entry(wl, listed, item_pos(item, a.n_qt, a.mul_qt, HP, a.mul_hp).slot, a.n_tiles) >> 16);   // live key tiles: score tile j at TMEM column j*64
         ptx::mbar_wait(&bar->q_full, par);
         ptx::mbar_wait(&bar->s_empty, par ^ 1);            // previous item's scores have been consumed
         ptx::tc_fence_after();
@@ -273,16 +287,18 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     auto fetch_mask = [&](int item_n) {
       if (D128) return;
 #pragma unroll
-      for (int j = 0; j < MAX_TILES; ++j) mb[j] = 0;
-      if (!a.mask || item_n >= a.n_items) return;
-      const uint32_t ent_n = slot_entry(wl, listed, (item_n / a.n_qt) / HP, a.n_tiles);
+      for (int j = 0; j < MAX_TILES; ++j) mb[j] = 1;                 // 0 = this lane's key of live tile j takes part
+      if (item_n >= a.n_items) return;
+      const uint32_t ent_n = slot_entry(wl, listed, item_pos(item_n, a.n_qt, a.mul_qt, HP, a.mul_hp).slot, a.n_tiles);
       const uint8_t* mrow = a.mask + static_cast<long>(ent_n & 0xFFFF) * a.m_stride_b;
+      const int lim = a.mask ? min(a.S, a.mask_S) : 0;                // keys below it have a mask byte
       uint32_t m = ent_n >> 16;
 #pragma unroll
       for (int j = 0; j < MAX_TILES; ++j) {
         if (m) {
           const int key = (__ffs(m) - 1) * TKEYS + quad * 32 + lane;
-          if (key < a.S && key < a.mask_S) mb[j] = mrow[key];
+          if (key < lim) mb[j] = mrow[key];
+          else if (key < a.S) mb[j] = 0;
           m &= m - 1;
         }
       }
@@ -290,8 +306,9 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     fetch_mask(blockIdx.x);
     for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
       const uint32_t par = it & 1;
-      const int qt = item % a.n_qt, r = item / a.n_qt, hp = r % HP;
-      const uint32_t ent = slot_entry(wl, listed, r / HP, a.n_tiles);
+      const ItemPos ip = item_pos(item, a.n_qt, a.mul_qt, HP, a.mul_hp);
+      const int qt = ip.qt, hp = ip.hp;
+      const uint32_t ent = slot_entry(wl, listed, ip.slot, a.n_tiles);
       const int b = ent & 0xFFFF;
       const uint32_t live = ent >> 16;
       // validity of this lane's key in every tile (key-padding mask: multi_head.py:441-449)
@@ -300,15 +317,8 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       uint32_t valid = 0;             // bit j: this lane's key of the j-th LIVE tile takes part (D128: lies inside [0, S))
       uint32_t vis[D128 ? MAX_TILES : 1];            // D128: bit c of vis[j] = query c of this tile SEES the key (mask != 0)
       if (!D128) {
-        uint32_t m = live;
 #pragma unroll
-        for (int j = 0; j < MAX_TILES; ++j) {
-          if (m) {
-            const int key = (__ffs(m) - 1) * TKEYS + quad * 32 + lane;
-            valid |= static_cast<uint32_t>(key < a.S && mb[j] == 0) << j;
-            m &= m - 1;
-          }
-        }
+        for (int j = 0; j < MAX_TILES; ++j) valid |= static_cast<uint32_t>(mb[j] == 0) << j;
       } else {
         int j = 0;
         for (uint32_t m = live; m; m &= m - 1, ++j) {
@@ -574,6 +584,13 @@ int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st) {
   if (p->weights) TNT_CUDA(cudaMemsetAsync(p->weights, 0, sizeof(float) * static_cast<size_t>(p->B) * p->T * p->S, st));
   a.n_qt = (p->T + atc::TQ - 1) / atc::TQ;
   a.n_items = p->B * (d128 ? p->H : p->H / 2) * a.n_qt;
+  {
+    const int hp = d128 ? p->H : p->H / 2;
+    // fast_div is exact while x * d < 2^32 (x < n_items, d <= max(n_qt, hp)); xattn_tc_supported keeps B <= 65535
+    TNT_CHECK_ARG(static_cast<uint64_t>(a.n_items) * std::max(a.n_qt, hp) < (1ull << 32), "xattn_tc: too many work items");
+    a.mul_qt = a.n_qt > 1 ? static_cast<uint32_t>((1ull << 32) / a.n_qt) + 1u : 0u;
+    a.mul_hp = hp > 1 ? static_cast<uint32_t>((1ull << 32) / hp) + 1u : 0u;
+  }
   a.n_tiles = (p->S + atc::TKEYS - 1) / atc::TKEYS;
   static PerDeviceOnce attr_once;
   if (attr_once.first()) {
