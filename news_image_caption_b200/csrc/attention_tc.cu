@@ -3,13 +3,14 @@
 // softmax, PV).  The extra bias_k / zero rows are ordinary k/v rows here (the engine materialises them
 // once per batch, engine_fwd.cu), the mask covers the first `mask_S` keys only.
 //
-// One work item = (batch row b, PAIR of heads, tile of <= 32 queries); persistent CTAs, 10 warps:
+// One work item = (batch row b, PAIR of heads, tile of <= 32 queries); persistent CTAs, 18 warps:
 //   warp 0      TMA producer: Q pair, then 128-key K tiles and V tiles (128B swizzle) through mbarrier rings
 //   warp 1      one thread issues tcgen05.mma:
 //                 S^T[keys, q] = K_h[keys, 64] . Q_h[q, 64]^T   (M=128 keys, N=32 queries, per head)
 //                 O^T[(h,d), (h',q)] += V[(h,d), keys] . P[keys, (h',q)]   (M=128 = 2 heads x 64 dims, N=64)
 //               -> every score tile of the item stays in TMEM (<= 7 tiles x 64 columns), O^T in 64 more
-//   warps 2-9   softmax: lane = key, exact two-pass softmax in fp32 straight out of TMEM (column max with
+//   warps 2-17  softmax (the serial chain of the kernel, so the 32 queries of a head are split over TWO warps of 16
+//               columns each: 4 lane quadrants x 2 heads x 2 column halves): lane = key, exact two-pass softmax in fp32 straight out of TMEM (column max with
 //               redux.sync + one cross-warp exchange), P written to smem as the bf16 MN-major B operand,
 //               epilogue: O^T * 1/l -> global (lanes = consecutive channels, coalesced)
 // Zero padding waste in M for the score MMAs (keys fill M), 2x waste (cross-head blocks) in the PV MMAs.
@@ -24,7 +25,9 @@ int make_tmap_bf16_3d(CUtensorMap* tm, const void* base, long d0, long d1, long 
                       int box0, int box1, int box2);
 
 namespace atc {
-constexpr int kThreads = 320;
+constexpr int kSoftWarps = 16;                    // 4 TMEM lane quadrants x 2 heads x 2 halves of the 32 query columns
+constexpr int kThreads = (2 + kSoftWarps) * 32;
+constexpr int CW = 16;                            // score columns (queries) per softmax warp
 constexpr int TQ = 32, TKEYS = 128, D = 64;
 constexpr int KS = 3, VS = 2, PS = 2;
 constexpr int Q_BYTES = 2 * TQ * 128;             // two heads
@@ -148,12 +151,12 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     ptx::mbar_init(&bar->q_full, 1);
     ptx::mbar_init(&bar->q_empty, 1);
     ptx::mbar_init(&bar->s_ready, 1);
-    ptx::mbar_init(&bar->s_empty, 8);
+    ptx::mbar_init(&bar->s_empty, kSoftWarps);
     ptx::mbar_init(&bar->o_ready, 1);
-    ptx::mbar_init(&bar->o_empty, 8);
+    ptx::mbar_init(&bar->o_empty, kSoftWarps);
     for (int i = 0; i < KS; ++i) { ptx::mbar_init(&bar->k_full[i], 1); ptx::mbar_init(&bar->k_empty[i], 1); }
     for (int i = 0; i < VS; ++i) { ptx::mbar_init(&bar->v_full[i], 1); ptx::mbar_init(&bar->v_empty[i], 1); }
-    for (int i = 0; i < PS; ++i) { ptx::mbar_init(&bar->p_ready[i], 8); ptx::mbar_init(&bar->p_empty[i], 1); }
+    for (int i = 0; i < PS; ++i) { ptx::mbar_init(&bar->p_ready[i], kSoftWarps); ptx::mbar_init(&bar->p_empty[i], 1); }
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<512>(&bar->tmem);
@@ -274,7 +277,11 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   } else {
     // ------------------------------------------------------------------ softmax + epilogue warps
     const int quad = warp & 3;                 // TMEM lane quadrant
-    const int hd = (warp - 2) >> 2;            // which head's 32 score columns this warp owns
+    const int grp = (warp - 2) >> 2;           // 0..3
+    const int hd = grp >> 1;                   // which head's score columns this warp works on
+    const int half = grp & 1;                  //   and which 16 of its 32 queries
+    const int cb = half * CW;                  // first query column of this warp inside the head's 32
+    const int l16 = lane & (CW - 1);
     const uint32_t lane_base = static_cast<uint32_t>(quad * 32) << 16;
     float* red_max = red + (hd * 4 + quad) * 32;
     float* red_sum = red + 256 + (hd * 4 + quad) * 32;
@@ -347,40 +354,40 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       ptx::mbar_wait(&bar->s_ready, par);
       ptx::tc_fence_after();
       // ---- pass 1: column maxima over the keys
-      float mx[32];
+      float mx[CW];
 #pragma unroll
-      for (int c = 0; c < 32; ++c) mx[c] = -INFINITY;
+      for (int c = 0; c < CW; ++c) mx[c] = -INFINITY;
       for (int i = 0; i < nl && score_warp; ++i) {
-        uint32_t v[32];
-        ptx::tmem_ld_32x32(tmem + lane_base + i * 64 + hd * 32, v);
+        uint32_t v[CW];
+        ptx::tmem_ld_32x16(tmem + lane_base + i * 64 + hd * 32 + cb, v);
         ptx::tmem_ld_wait();
         if ((valid >> i) & 1) {
 #pragma unroll
-          for (int c = 0; c < 32; ++c)
-            mx[c] = fmaxf(mx[c], (!D128 || ((vis[D128 ? i : 0] >> c) & 1)) ? __uint_as_float(v[c]) : neg_raw);
+          for (int c = 0; c < CW; ++c)
+            mx[c] = fmaxf(mx[c], (!D128 || ((vis[D128 ? i : 0] >> (cb + c)) & 1)) ? __uint_as_float(v[c]) : neg_raw);
         }
       }
       float mine = -INFINITY;
 #pragma unroll
-      for (int c = 0; c < 32; ++c) {
+      for (int c = 0; c < CW; ++c) {
         const float w = redux_max(mx[c]);
         if (lane == c) mine = w;
       }
-      red_max[lane] = mine;
-      named_bar(1 + hd, 128);
-      float col_max;                     // max of the unscaled scores of column (query) `lane`
+      if (lane < CW) red_max[cb + lane] = mine;
+      named_bar(1 + hd, 256);            // the 8 warps of this head
+      float col_max;                     // max of the unscaled scores of column (query) cb + (lane & 15)
       {
-        const float* rm = red + hd * 128;
-        const float m4 = fmaxf(fmaxf(rm[lane], rm[32 + lane]), fmaxf(rm[64 + lane], rm[96 + lane]));
+        const float* rm = red + hd * 128 + cb + l16;
+        const float m4 = fmaxf(fmaxf(rm[0], rm[32]), fmaxf(rm[64], rm[96]));
         const float ms = (m4 == -INFINITY) ? 0.f : m4;
         col_max = ms;
 #pragma unroll
-        for (int c = 0; c < 32; ++c) mx[c] = __shfl_sync(0xffffffffu, ms, c) * a.scale_log2e;
+        for (int c = 0; c < CW; ++c) mx[c] = __shfl_sync(0xffffffffu, ms, c) * a.scale_log2e;
       }
       // ---- pass 2: probabilities -> smem (bf16, MN-major B operand), running column sums
-      float ls[32];
+      float ls[CW];
 #pragma unroll
-      for (int c = 0; c < 32; ++c) ls[c] = 0.f;
+      for (int c = 0; c < CW; ++c) ls[c] = 0.f;
       uint32_t mleft = live;
       for (int i = 0; i < nl; ++i, mleft &= mleft - 1) {
         const int tile = __ffs(mleft) - 1;                    // key tile the i-th score tile belongs to
@@ -391,28 +398,28 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           if (++ps == PS) { ps = 0; pph ^= 1; }
           continue;
         }
-        uint32_t v[32];
-        ptx::tmem_ld_32x32(tmem + lane_base + i * 64 + hd * 32, v);
+        uint32_t v[CW];
+        ptx::tmem_ld_32x16(tmem + lane_base + i * 64 + hd * 32 + cb, v);
         ptx::tmem_ld_wait();
         const bool ok = (valid >> i) & 1;
         if (D128) {                                            // masked (query, key) pairs carry the -1e9 fill, not "absent"
 #pragma unroll
-          for (int c = 0; c < 32; ++c)
-            if (!((vis[D128 ? i : 0] >> c) & 1)) v[c] = __float_as_uint(neg_raw);
+          for (int c = 0; c < CW; ++c)
+            if (!((vis[D128 ? i : 0] >> (cb + c)) & 1)) v[c] = __float_as_uint(neg_raw);
         }
-        uint32_t pk[16];
+        uint32_t pk[CW / 2];
 #pragma unroll
-        for (int c = 0; c < 16; ++c) pk[c] = 0u;
+        for (int c = 0; c < CW / 2; ++c) pk[c] = 0u;
         if (ok)                                    // (a key outside the row contributes nothing: only a ragged tile diverges)
 #pragma unroll
-        for (int c = 0; c < 32; c += 2) {
+        for (int c = 0; c < CW; c += 2) {
           float p0 = ex2_fast(fmaf(__uint_as_float(v[c]), a.scale_log2e, -mx[c]));
           float p1 = ex2_fast(fmaf(__uint_as_float(v[c + 1]), a.scale_log2e, -mx[c + 1]));
           ls[c] += p0;
           ls[c + 1] += p1;
           if (DROP) {
             const unsigned long long i0 =
-                ((static_cast<unsigned long long>(b) * a.H + hp * 2 + hd) * a.T + qt * TQ + c) * a.S + tile * TKEYS + quad * 32 + lane;
+                ((static_cast<unsigned long long>(b) * a.H + hp * 2 + hd) * a.T + qt * TQ + cb + c) * a.S + tile * TKEYS + quad * 32 + lane;
             p0 = drop_val(a.drop, i0, p0);
             p1 = drop_val(a.drop, i0 + a.S, p1);
           }
@@ -422,8 +429,8 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const int row = quad * 32 + lane;
         uint8_t* prow = sP + ps * P_STAGE + row * 128;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int chunk = (hd * 4 + j) ^ (row & 7);             // 128-byte swizzle
+        for (int j = 0; j < CW / 8; ++j) {
+          const int chunk = (hd * 4 + half * (CW / 8) + j) ^ (row & 7);   // 128-byte swizzle
           *reinterpret_cast<uint4*>(prow + chunk * 16) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
         }
         ptx::fence_proxy_async();
@@ -439,7 +446,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       // butterfly reduce-scatter: at distance ofs a lane keeps the half of its columns that its own bit selects and hands the
       // other half to its partner -- 31 shuffles for the 32 sums (a full warp_sum per column: 160); lane L ends with column L
 #pragma unroll
-      for (int ofs = 16; ofs >= 1; ofs >>= 1) {
+      for (int ofs = CW / 2; ofs >= 1; ofs >>= 1) {
         const bool up = (lane & ofs) != 0;
 #pragma unroll
         for (int i = 0; i < ofs; ++i) {
@@ -448,35 +455,36 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           ls[i] = keep + __shfl_xor_sync(0xffffffffu, send, ofs);
         }
       }
-      red_sum[lane] = ls[0];
-      named_bar(3, 256);                 // the epilogue reads the sums of BOTH head groups
+      ls[0] += __shfl_xor_sync(0xffffffffu, ls[0], CW);     // lanes L and L ^ 16 hold the two halves of column L & 15
+      if (lane < CW) red_sum[cb + lane] = ls[0];
+      named_bar(3, kSoftWarps * 32);     // the epilogue reads the sums of BOTH head groups
       if (a.weights) {
         // ---- pass 3 (last decoder layer only): head-averaged attention weights.  The scores are still resident in TMEM
         // and the normalisers are final, so every probability is rebuilt exactly as pass 2 made it, scaled by
         // 1 / (l * H) and added to weights[b, t, key]: the 8 head pairs of a caption land on the same row through
         // red.global.add (lanes = consecutive keys: one 128-byte reduction per warp and query).  Masked keys add nothing.
-        const float* rsl = red + 256 + hd * 128;
-        const float lsum = rsl[lane] + rsl[32 + lane] + rsl[64 + lane] + rsl[96 + lane];
-        const float my_inv = lsum > 0.f ? a.inv_heads / lsum : 0.f;          // column (query) `lane`
+        const float* rsl = red + 256 + hd * 128 + cb + l16;
+        const float lsum = rsl[0] + rsl[32] + rsl[64] + rsl[96];
+        const float my_inv = lsum > 0.f ? a.inv_heads / lsum : 0.f;          // column (query) cb + (lane & 15)
         uint32_t ml = live;
         for (int i = 0; i < nl; ++i, ml &= ml - 1) {
           const int tile = __ffs(ml) - 1;
-          uint32_t v[32];
-          ptx::tmem_ld_32x32(tmem + lane_base + i * 64 + hd * 32, v);
+          uint32_t v[CW];
+          ptx::tmem_ld_32x16(tmem + lane_base + i * 64 + hd * 32 + cb, v);
           ptx::tmem_ld_wait();
           const bool ok = (valid >> i) & 1;
           const int key = tile * TKEYS + quad * 32 + lane;
-          float* wrow = a.weights + (static_cast<long>(b) * a.T + qt * TQ) * a.S + key;
+          float* wrow = a.weights + (static_cast<long>(b) * a.T + qt * TQ + cb) * a.S + key;
 #pragma unroll
-          for (int c = 0; c < 32; ++c) {
+          for (int c = 0; c < CW; ++c) {
             const float inv = __shfl_sync(0xffffffffu, my_inv, c);
             float pw = ex2_fast(fmaf(__uint_as_float(v[c]), a.scale_log2e, -mx[c]));
             if (DROP) {
               const unsigned long long i0 =
-                  ((static_cast<unsigned long long>(b) * a.H + hp * 2 + hd) * a.T + qt * TQ + c) * a.S + tile * TKEYS + quad * 32 + lane;
+                  ((static_cast<unsigned long long>(b) * a.H + hp * 2 + hd) * a.T + qt * TQ + cb + c) * a.S + tile * TKEYS + quad * 32 + lane;
               pw = drop_val(a.drop, i0, pw);
             }
-            if (ok && qt * TQ + c < a.T) atomicAdd(wrow + static_cast<long>(c) * a.S, pw * inv);
+            if (ok && qt * TQ + cb + c < a.T) atomicAdd(wrow + static_cast<long>(c) * a.S, pw * inv);
           }
         }
         ptx::tc_fence_before();
@@ -484,28 +492,28 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         if (lane == 0) ptx::mbar_arrive(&bar->s_empty);
       }
       if (a.lse && quad == 0) {          // log-sum-exp of the scaled scores, saved for the backward pass
-        const float* rsl = red + 256 + hd * 128;
-        const float l = rsl[lane] + rsl[32 + lane] + rsl[64 + lane] + rsl[96 + lane];
-        const int t = qt * TQ + lane;
-        if (t < a.T && score_warp)
+        const float* rsl = red + 256 + hd * 128 + cb + l16;
+        const float l = rsl[0] + rsl[32] + rsl[64] + rsl[96];
+        const int t = qt * TQ + cb + lane;
+        if (lane < CW && t < a.T && score_warp)
           a.lse[(static_cast<long>(b) * a.H + (D128 ? hp : hp * 2 + hd)) * a.T + t] = l > 0.f ? col_max * a.scale + __logf(l) : INFINITY;
       }
-      // ---- epilogue: O^T rows of this quadrant belong to head (quad / 2); this warp takes 16 queries
+      // ---- epilogue: O^T rows of this quadrant belong to head (quad / 2); each of the quadrant's 4 warps takes 8 queries
       const int oh = D128 ? 0 : quad >> 1;
-      const int q0 = hd * 16;
-      // 1 / l of query q0 + (lane & 15), handed out below with one shuffle per query (a division and four shared-memory
+      const int q0 = grp * 8;
+      // 1 / l of query q0 + (lane & 7), handed out below with one shuffle per query (a division and four shared-memory
       // loads per ELEMENT made the epilogue a quarter of the kernel's instructions)
       float inv_mine;
       {
         const float* rs = red + 256 + oh * 128;
-        const int q = q0 + (lane & 15);
+        const int q = q0 + (lane & 7);
         const float l = rs[q] + rs[32 + q] + rs[64 + q] + rs[96 + q];
         inv_mine = l > 0.f ? 1.f / l : 0.f;
       }
       ptx::mbar_wait(&bar->o_ready, par);
       ptx::tc_fence_after();
-      uint32_t o[16];
-      ptx::tmem_ld_32x16(tmem + lane_base + O_COL + oh * 32 + q0, o);      // D128: O^T columns 0..31 = the 32 queries
+      uint32_t o[8];
+      ptx::tmem_ld_32x8(tmem + lane_base + O_COL + oh * 32 + q0, o);       // D128: O^T columns 0..31 = the 32 queries
       ptx::tmem_ld_wait();
       ptx::tc_fence_before();
       __syncwarp();
@@ -515,12 +523,12 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                   static_cast<long>(qt * TQ + q0) * a.o_stride_t;
       const int n_q = a.T - (qt * TQ + q0);                                  // queries of this block that exist
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
+      for (int j = 0; j < 8; ++j) {
         const float inv = __shfl_sync(0xffffffffu, inv_mine, j);
         if (j < n_q) *out = __float2bfloat16_rn(__uint_as_float(o[j]) * inv);
         out += a.o_stride_t;
       }
-      named_bar(3, 256);                 // red[] is rewritten by the next item only after everyone has read it
+      named_bar(3, kSoftWarps * 32);                 // red[] is rewritten by the next item only after everyone has read it
     }
   }
   ptx::tc_fence_before();
