@@ -29,14 +29,17 @@ constexpr int kSoftWarps = 16;                    // 4 TMEM lane quadrants x 2 h
 constexpr int kThreads = (2 + kSoftWarps) * 32;
 constexpr int CW = 16;                            // score columns (queries) per softmax warp
 constexpr int TQ = 32, TKEYS = 128, D = 64;
-constexpr int KS = 3, VS = 2, PS = 2;
+// K and V tiles share ONE ring, filled in consumption order (the item's K tiles, then its V tiles): a K tile is dead as soon
+// as its score product has been issued, so the item's V tiles -- and, behind the PV products, the NEXT item's K tiles --
+// stream in while the softmax warps work; with separate 3 + 2 stage rings every round of loads sat in their serial chain
+constexpr int KVS = 5, PS = 2;
 constexpr int Q_BYTES = 2 * TQ * 128;             // two heads
 constexpr int KV_STAGE = 2 * TKEYS * 128;         // two heads x 128 keys x 128 B
 constexpr int P_STAGE = TKEYS * 128;              // 128 keys x 64 (h,q) bf16
 constexpr int MAX_TILES = 7;
 constexpr uint32_t O_COL = 448;
 constexpr int kListBytes = 2048 * 4 + 128 + 1024;  // sorted work list + histogram (+ the alignment slack of the base)
-constexpr int SMEM_BYTES = Q_BYTES + KS * KV_STAGE + VS * KV_STAGE + PS * P_STAGE + 4096 + 2048 + kListBytes;
+constexpr int SMEM_BYTES = Q_BYTES + KVS * KV_STAGE + PS * P_STAGE + 4096 + 2048 + kListBytes;
 
 struct Args {
   float* lse; float scale;
@@ -50,6 +53,7 @@ struct Args {
   const uint32_t* tile_live;                      // optional [B]: bit i set = key tile i of batch row b holds an un-masked key
   float* weights;                                 // optional [B, T, S] fp32, ZEROED by the launcher: head-averaged probabilities
   float inv_heads;                                //   (multi_head.py:478-482), accumulated with red.global.add by a third pass
+  long long* trace;                               // debug (tnt_debug_xattn_trace): clock64 stamps of CTAs 0..3, [cta][role 0..2][item 0..7][8]
   long m_stride_t;                                // D128 / V2 mask: byte stride over the query index (0 = one mask row per batch entry)
 };
 
@@ -99,9 +103,16 @@ __device__ __forceinline__ ItemPos item_pos(int item, int n_qt, uint32_t mul_qt,
   return p;
 }
 
+#define XTRACE(role, slot)                                                                          \
+  do {                                                                                              \
+    if (a.trace && blockIdx.x < 4 && it < 8 && lane == 0)                                           \
+      a.trace[((blockIdx.x * 3 + (role)) * 8 + it) * 8 + (slot)] = clock64();                       \
+  } while (0)
+
 struct Bars {
-  uint64_t q_full, q_empty, s_ready, s_empty, o_ready, o_empty;
-  uint64_t k_full[KS], k_empty[KS], v_full[VS], v_empty[VS], p_ready[PS], p_empty[PS];
+  uint64_t q_full, q_empty, s_empty, o_ready, o_empty;
+  uint64_t s_tile[MAX_TILES];       // score tile i of the current item has been written (one phase per item that HAS a tile i)
+  uint64_t kv_full[KVS], kv_empty[KVS], p_ready[PS], p_empty[PS];
   uint32_t tmem;
 };
 
@@ -133,11 +144,10 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;
-  uint8_t* sK = sQ + Q_BYTES;
-  uint8_t* sV = sK + KS * KV_STAGE;
-  uint8_t* sP = sV + VS * KV_STAGE;
-  float* red = reinterpret_cast<float*>(sP + PS * P_STAGE);          // [2 heads][4 quadrants][32] x 2 (max, sum)
-  Bars* bar = reinterpret_cast<Bars*>(reinterpret_cast<uint8_t*>(red) + 4096);
+  uint8_t* sKV = sQ + Q_BYTES;
+  uint8_t* sP = sKV + KVS * KV_STAGE;
+  float* red0 = reinterpret_cast<float*>(sP + PS * P_STAGE);         // [item parity][max, sum][2 heads][4 quadrants][32]
+  Bars* bar = reinterpret_cast<Bars*>(reinterpret_cast<uint8_t*>(red0) + 4096);
   uint32_t* wl = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(bar) + 2048);
   int* wl_hist = reinterpret_cast<int*>(wl + kMaxList);
   const bool listed = a.tile_live != nullptr && a.B <= kMaxList;
@@ -150,12 +160,11 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     ptx::prefetch_tmap(&tmV);
     ptx::mbar_init(&bar->q_full, 1);
     ptx::mbar_init(&bar->q_empty, 1);
-    ptx::mbar_init(&bar->s_ready, 1);
+    for (int i = 0; i < MAX_TILES; ++i) ptx::mbar_init(&bar->s_tile[i], 1);
     ptx::mbar_init(&bar->s_empty, kSoftWarps);
     ptx::mbar_init(&bar->o_ready, 1);
     ptx::mbar_init(&bar->o_empty, kSoftWarps);
-    for (int i = 0; i < KS; ++i) { ptx::mbar_init(&bar->k_full[i], 1); ptx::mbar_init(&bar->k_empty[i], 1); }
-    for (int i = 0; i < VS; ++i) { ptx::mbar_init(&bar->v_full[i], 1); ptx::mbar_init(&bar->v_empty[i], 1); }
+    for (int i = 0; i < KVS; ++i) { ptx::mbar_init(&bar->kv_full[i], 1); ptx::mbar_init(&bar->kv_empty[i], 1); }
     for (int i = 0; i < PS; ++i) { ptx::mbar_init(&bar->p_ready[i], kSoftWarps); ptx::mbar_init(&bar->p_empty[i], 1); }
     ptx::fence_barrier_init();
   }
@@ -183,8 +192,8 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     {   // the whole warp walks the loops, ONE elected lane issues: operands stay in uniform registers (a single divergent
         // lane paid an ELECT + 5 R2UR.BROADCAST + descriptor arithmetic in vector registers per tcgen05.mma / bulk copy)
       const bool leader = ptx::elect_one();
-      int ks = 0, vs = 0;
-      uint32_t kph = 0, vph = 0, it = 0;
+      int ks = 0;
+      uint32_t kph = 0, it = 0;
       for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
         const ItemPos ip = item_pos(item, a.n_qt, a.mul_qt, HP, a.mul_hp);
         const int qt = ip.qt, hp = ip.hp;
@@ -193,24 +202,26 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const uint32_t live = ent >> 16;
         const int c0 = hp * 2 * D;
         ptx::mbar_wait(&bar->q_empty, (it & 1) ^ 1);
+        XTRACE(2, 0);
         if (leader) ptx::mbar_arrive_expect_tx(&bar->q_full, Q_BYTES);
         if (leader) ptx::tma_load_3d(sQ, &tmQ, &bar->q_full, c0, b, qt * TQ);
         if (leader) ptx::tma_load_3d(sQ + TQ * 128, &tmQ, &bar->q_full, c0 + D, b, qt * TQ);
         for (uint32_t m = live; m; m &= m - 1) {
           const int i = __ffs(m) - 1;
-          ptx::mbar_wait(&bar->k_empty[ks], kph ^ 1);
-          if (leader) ptx::mbar_arrive_expect_tx(&bar->k_full[ks], KV_STAGE);
-          if (leader) ptx::tma_load_3d(sK + ks * KV_STAGE, &tmK, &bar->k_full[ks], c0, b, i * TKEYS);
-          if (leader) ptx::tma_load_3d(sK + ks * KV_STAGE + TKEYS * 128, &tmK, &bar->k_full[ks], c0 + D, b, i * TKEYS);
-          if (++ks == KS) { ks = 0; kph ^= 1; }
+          ptx::mbar_wait(&bar->kv_empty[ks], kph ^ 1);
+          if (leader) ptx::mbar_arrive_expect_tx(&bar->kv_full[ks], KV_STAGE);
+          if (leader) ptx::tma_load_3d(sKV + ks * KV_STAGE, &tmK, &bar->kv_full[ks], c0, b, i * TKEYS);
+          if (leader) ptx::tma_load_3d(sKV + ks * KV_STAGE + TKEYS * 128, &tmK, &bar->kv_full[ks], c0 + D, b, i * TKEYS);
+          if (++ks == KVS) { ks = 0; kph ^= 1; }
         }
         for (uint32_t m = live; m; m &= m - 1) {
           const int i = __ffs(m) - 1;
-          ptx::mbar_wait(&bar->v_empty[vs], vph ^ 1);
-          if (leader) ptx::mbar_arrive_expect_tx(&bar->v_full[vs], KV_STAGE);
-          if (leader) ptx::tma_load_3d(sV + vs * KV_STAGE, &tmV, &bar->v_full[vs], c0, b, i * TKEYS);
-          if (leader) ptx::tma_load_3d(sV + vs * KV_STAGE + TKEYS * 128, &tmV, &bar->v_full[vs], c0 + D, b, i * TKEYS);
-          if (++vs == VS) { vs = 0; vph ^= 1; }
+          ptx::mbar_wait(&bar->kv_empty[ks], kph ^ 1);
+          if (leader) ptx::mbar_arrive_expect_tx(&bar->kv_full[ks], KV_STAGE);
+          if (leader) ptx::tma_load_3d(sKV + ks * KV_STAGE, &tmV, &bar->kv_full[ks], c0, b, i * TKEYS);
+          if (leader) ptx::tma_load_3d(sKV + ks * KV_STAGE + TKEYS * 128, &tmV, &bar->kv_full[ks], c0 + D, b, i * TKEYS);
+          if (++ks == KVS) { ks = 0; kph ^= 1; }
+          XTRACE(2, 1 + min(i, 6));
         }
       }
     }
@@ -222,19 +233,22 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const bool leader = ptx::elect_one();
       const uint32_t idesc_qk = ptx::umma_idesc_bf16(128, TQ, 0, 0);
       const uint32_t idesc_pv = ptx::umma_idesc_bf16(128, 2 * TQ, 1, 1);
-      int ks = 0, vs = 0, ps = 0;
-      uint32_t kph = 0, vph = 0, pph = 0, it = 0;
+      int ks = 0, ps = 0;
+      uint32_t kph = 0, pph = 0, it = 0;
       for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
         const uint32_t par = it & 1;
         const int nl = __popc(slot_entry(wl, listed, item_pos(item, a.n_qt, a.mul_qt, HP, a.mul_hp).slot, a.n_tiles) >> 16);   // live key tiles: score tile j at TMEM column j*64
+        XTRACE(1, 0);
         ptx::mbar_wait(&bar->q_full, par);
+        XTRACE(1, 1);
         ptx::mbar_wait(&bar->s_empty, par ^ 1);            // previous item's scores have been consumed
         ptx::tc_fence_after();
+        XTRACE(1, 2);
         const uint32_t q_addr = ptx::smem_u32(sQ);
         for (int i = 0; i < nl; ++i) {
-          ptx::mbar_wait(&bar->k_full[ks], kph);
+          ptx::mbar_wait(&bar->kv_full[ks], kph);
           ptx::tc_fence_after();
-          const uint32_t k_addr = ptx::smem_u32(sK + ks * KV_STAGE);
+          const uint32_t k_addr = ptx::smem_u32(sKV + ks * KV_STAGE);
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
 #pragma unroll
@@ -245,18 +259,22 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
               if (leader) ptx::umma_bf16_ss(tmem + i * 64 + (D128 ? 0 : h * 32), ad, bd, idesc_qk, D128 ? (h | k) != 0 : k != 0);
             }
           }
-          if (leader) ptx::umma_commit(&bar->k_empty[ks]);
-          if (++ks == KS) { ks = 0; kph ^= 1; }
+          if (leader) ptx::umma_commit(&bar->kv_empty[ks]);
+          if (leader) ptx::umma_commit(&bar->s_tile[i]);     // pass 1 starts on tile 0 while the later K tiles are still in flight
+          if (++ks == KVS) { ks = 0; kph ^= 1; }
         }
         if (leader) ptx::umma_commit(&bar->q_empty);
-        if (leader) ptx::umma_commit(&bar->s_ready);
+        XTRACE(1, 3);
         ptx::mbar_wait(&bar->o_empty, par ^ 1);            // previous item's output has been read
         ptx::tc_fence_after();
+        XTRACE(1, 4);
         for (int i = 0; i < nl; ++i) {
-          ptx::mbar_wait(&bar->v_full[vs], vph);
+          ptx::mbar_wait(&bar->kv_full[ks], kph);
+          if (i == 0) XTRACE(1, 5);
           ptx::mbar_wait(&bar->p_ready[ps], pph);
           ptx::tc_fence_after();
-          const uint32_t v_addr = ptx::smem_u32(sV + vs * KV_STAGE);
+          if (i == 0) XTRACE(1, 6);
+          const uint32_t v_addr = ptx::smem_u32(sKV + ks * KV_STAGE);
           const uint32_t p_addr = ptx::smem_u32(sP + ps * P_STAGE);
 #pragma unroll
           for (int k = 0; k < TKEYS / 16; ++k) {
@@ -265,12 +283,13 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             const uint64_t bd = ptx::umma_smem_desc(p_addr + k * 2048, 16, 1024);
             if (leader) ptx::umma_bf16_ss(tmem + O_COL, ad, bd, idesc_pv, (i | k) != 0);
           }
-          if (leader) ptx::umma_commit(&bar->v_empty[vs]);
+          if (leader) ptx::umma_commit(&bar->kv_empty[ks]);
           if (leader) ptx::umma_commit(&bar->p_empty[ps]);
-          if (++vs == VS) { vs = 0; vph ^= 1; }
+          if (++ks == KVS) { ks = 0; kph ^= 1; }
           if (++ps == PS) { ps = 0; pph ^= 1; }
         }
         if (leader) ptx::umma_commit(&bar->o_ready);
+        XTRACE(1, 7);
       }
     }
     __syncwarp();
@@ -283,10 +302,11 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int cb = half * CW;                  // first query column of this warp inside the head's 32
     const int l16 = lane & (CW - 1);
     const uint32_t lane_base = static_cast<uint32_t>(quad * 32) << 16;
-    float* red_max = red + (hd * 4 + quad) * 32;
-    float* red_sum = red + 256 + (hd * 4 + quad) * 32;
+    // red[] is double buffered by item parity: a warp that runs ahead into the next item writes the OTHER copy, and cannot
+    // reach the item after that before every warp has passed this item's barriers (no end-of-item barrier needed)
     int ps = 0;
     uint32_t pph = 0, it = 0;
+    uint32_t sph = 0;                          // bit i: parity of the next phase of score-tile barrier i
     // key-padding bytes of this lane's key in every live tile of an item (head pairs): fetched one item AHEAD, behind the
     // previous item's pass 2, so the global-load latency is not part of the softmax warps' serial chain (15 % of their
     // stall samples when the bytes were loaded at the top of the item)
@@ -313,6 +333,10 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     fetch_mask(blockIdx.x);
     for (int item = blockIdx.x; item < a.n_items; item += gridDim.x, ++it) {
       const uint32_t par = it & 1;
+      float* red = red0 + par * 512;
+      float* red_max = red + (hd * 4 + quad) * 32;
+      float* red_sum = red + 256 + (hd * 4 + quad) * 32;
+      if (warp == 2) XTRACE(0, 0);
       const ItemPos ip = item_pos(item, a.n_qt, a.mul_qt, HP, a.mul_hp);
       const int qt = ip.qt, hp = ip.hp;
       const uint32_t ent = slot_entry(wl, listed, ip.slot, a.n_tiles);
@@ -351,13 +375,15 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
       }
       const float neg_raw = -1e9f / a.scale;         // raw-score value whose scaled form is the reference's -1e9 fill
-      ptx::mbar_wait(&bar->s_ready, par);
-      ptx::tc_fence_after();
+      if (warp == 2) XTRACE(0, 1);
       // ---- pass 1: column maxima over the keys
       float mx[CW];
 #pragma unroll
       for (int c = 0; c < CW; ++c) mx[c] = -INFINITY;
       for (int i = 0; i < nl && score_warp; ++i) {
+        ptx::mbar_wait(&bar->s_tile[i], (sph >> i) & 1);
+        ptx::tc_fence_after();
+        if (warp == 2 && i == 0) XTRACE(0, 2);
         uint32_t v[CW];
         ptx::tmem_ld_32x16(tmem + lane_base + i * 64 + hd * 32 + cb, v);
         ptx::tmem_ld_wait();
@@ -367,6 +393,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             mx[c] = fmaxf(mx[c], (!D128 || ((vis[D128 ? i : 0] >> (cb + c)) & 1)) ? __uint_as_float(v[c]) : neg_raw);
         }
       }
+      sph ^= (1u << nl) - 1u;
       float mine = -INFINITY;
 #pragma unroll
       for (int c = 0; c < CW; ++c) {
@@ -374,6 +401,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         if (lane == c) mine = w;
       }
       if (lane < CW) red_max[cb + lane] = mine;
+      if (warp == 2) XTRACE(0, 3);
       named_bar(1 + hd, 256);            // the 8 warps of this head
       float col_max;                     // max of the unscaled scores of column (query) cb + (lane & 15)
       {
@@ -440,6 +468,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       ptx::tc_fence_before();
       __syncwarp();
+      if (warp == 2) XTRACE(0, 4);
       if (!a.weights && lane == 0) ptx::mbar_arrive(&bar->s_empty);        // score columns may be overwritten
       fetch_mask(item + gridDim.x);      // the next item's mask bytes: in flight through the column sums and the epilogue
       // column sums across the warp, then across the 4 quadrant warps of this head
@@ -458,6 +487,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       ls[0] += __shfl_xor_sync(0xffffffffu, ls[0], CW);     // lanes L and L ^ 16 hold the two halves of column L & 15
       if (lane < CW) red_sum[cb + lane] = ls[0];
       named_bar(3, kSoftWarps * 32);     // the epilogue reads the sums of BOTH head groups
+      if (warp == 2) XTRACE(0, 5);
       if (a.weights) {
         // ---- pass 3 (last decoder layer only): head-averaged attention weights.  The scores are still resident in TMEM
         // and the normalisers are final, so every probability is rebuilt exactly as pass 2 made it, scaled by
@@ -512,6 +542,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       ptx::mbar_wait(&bar->o_ready, par);
       ptx::tc_fence_after();
+      if (warp == 2) XTRACE(0, 6);
       uint32_t o[8];
       ptx::tmem_ld_32x8(tmem + lane_base + O_COL + oh * 32 + q0, o);       // D128: O^T columns 0..31 = the 32 queries
       ptx::tmem_ld_wait();
@@ -528,7 +559,7 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         if (j < n_q) *out = __float2bfloat16_rn(__uint_as_float(o[j]) * inv);
         out += a.o_stride_t;
       }
-      named_bar(3, kSoftWarps * 32);                 // red[] is rewritten by the next item only after everyone has read it
+      if (warp == 2) XTRACE(0, 7);
     }
   }
   ptx::tc_fence_before();
@@ -536,6 +567,10 @@ xattn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   if (warp == 2) ptx::tmem_dealloc<512>(tmem);
 }
 }  // namespace atc
+
+namespace atc { static long long* g_trace_buf = nullptr; }
+// debug: device buffer of 4 * 3 * 8 * 8 int64 that the next attention launches stamp with clock64 (NULL switches it off)
+extern "C" void tnt_debug_xattn_trace(long long* dev_buf) { atc::g_trace_buf = dev_buf; }
 
 namespace atc {
 __global__ void __launch_bounds__(256) tile_mask_kernel(const uint8_t* mask, long m_stride_b, int B, int S, int mask_S,
@@ -600,6 +635,7 @@ int xattn_fwd_tc(const tnt_xattn_params* p, cudaStream_t st) {
     a.mul_hp = hp > 1 ? static_cast<uint32_t>((1ull << 32) / hp) + 1u : 0u;
   }
   a.n_tiles = (p->S + atc::TKEYS - 1) / atc::TKEYS;
+  a.trace = atc::g_trace_buf;
   static PerDeviceOnce attr_once;
   if (attr_once.first()) {
     TNT_CUDA(cudaFuncSetAttribute(atc::xattn_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::SMEM_BYTES));
