@@ -60,10 +60,11 @@ struct tnt_decoder {
   void* emb_proj[TNT_MAX_CLUSTERS] = {};   // band projections [d, dim_i] in the engine dtype (training backward)
   int emb_dim[TNT_MAX_CLUSTERS] = {};
   std::vector<cudaEvent_t> stage_events;   // training: gradients of stage i are final (tnt_decoder_stream_wait_stage)
-  // training backward: the parameter-gradient tail of every linear (weight-norm backward, bias column sums) runs on a
-  // side stream beside the next data-gradient GEMM (those CTAs fit on the SMs a 128-CTA GEMM leaves partly empty)
+  // training backward: every parameter gradient (weight-gradient GEMM, weight-norm backward, bias column sum) runs on a
+  // side stream beside the latency-bound data-gradient chain (engine_train.cu)
   cudaStream_t side_stream = nullptr;
   cudaEvent_t side_fork = nullptr, side_join = nullptr;
+  std::vector<cudaEvent_t> side_layer_done;   // the parameter-gradient work of layer l has been issued up to here
   std::map<std::string, float*> grads; // training: fp32 gradient buffer per state_dict key (tnt_decoder_set_grad)
   // data-parallel training: embedding-row gradients go to a packed list instead of the dense band tables
   void* sparse_rows = nullptr; long long* sparse_meta = nullptr; int* sparse_count = nullptr; int sparse_capacity = 0;

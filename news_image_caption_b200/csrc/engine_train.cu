@@ -25,6 +25,21 @@ struct LayerAct {
   float* lse[TNT_MAX_SOURCES];
 };
 
+// Gradient tensors that a weight-gradient GEMM / bias column sum reads.  Those run on the parameter-gradient stream, beside
+// the data-gradient chain of the SAME and the NEXT layer, so each tensor has a buffer of its own (never rewritten inside a
+// layer) and the layers alternate between two sets: layer l's set is rewritten by layer l-2, which first waits for layer
+// l's parameter-gradient work.
+struct PGradBufs {
+  void *gffn;                                  // [N, d]    dL/d(fc2 output), dropout mask applied
+  void *dF;                                    // [N, ffn]  dL/d(fc1 output)
+  void *dX0;                                   // [N, d]    dL/d(context_fc output)
+  void *gop;                                   // [N, ns*d] dL/d(out_proj outputs), dropout mask applied
+  void *dQ;                                    // [N, ns*d]
+  void *gl2;                                   // [N, d]    dL/d(linear2 output), dropout mask applied
+  void *dlogits;                               // [N, ldl]
+  void *draw;                                  // [N, 2d]   dL/d(linear1 output)
+};
+
 struct TrainWs {
   void* emb;                                   // layer-0 input [N, d]
   LayerAct act[TNT_MAX_LAYERS];
@@ -32,11 +47,10 @@ struct TrainWs {
   void* dkv[TNT_MAX_SOURCES];
   uint32_t* tile_live[TNT_MAX_SOURCES];        // [B] live 128-key tiles per context entry
   void *Xbt, *dXbt;                            // decoder output / its gradient in B x T row order
-  void *gA, *gB, *gC, *gD;                     // [N, d] gradient ping-pong buffers
-  void *dQ, *dAO, *dCAT, *dCATp;               // [N, ns*d]
-  void *dF;                                    // [N, ffn]
-  void *raw, *draw;                            // [N, 2d]
-  void *dlogits;                               // [N, ldl]
+  void *gA, *gB, *gC, *gD;                     // [N, d] gradient ping-pong buffers (data-gradient chain only)
+  void *dAO, *dCAT, *dCATp;                    // [N, ns*d]
+  void *raw;                                   // [N, 2d]
+  PGradBufs pg[2];                             // what the parameter-gradient stream reads, by layer parity
   float* dW;                                   // fp32 scratch for weight-normed matrices / K-V / embedding grads
   size_t dW_floats;
   float* attn_scr;                             // [B, H, T, D] fp32
@@ -78,10 +92,13 @@ TrainWs carve_train(const tnt_decoder* D, int B, int T, const int* S, void* ws) 
   }
   w.Xbt = take(N * d * E); w.dXbt = take(N * d * E);
   w.gA = take(N * d * E); w.gB = take(N * d * E); w.gC = take(N * d * E); w.gD = take(N * d * E);
-  w.dQ = take(N * ns * d * E); w.dAO = take(N * ns * d * E); w.dCAT = take(N * ns * d * E); w.dCATp = take(N * ns * d * E);
-  w.dF = take(N * c.ffn * E);
-  w.raw = take(N * 2 * d * E); w.draw = take(N * 2 * d * E);
-  w.dlogits = take(N * D->max_ld_logits() * E);
+  w.dAO = take(N * ns * d * E); w.dCAT = take(N * ns * d * E); w.dCATp = take(N * ns * d * E);
+  w.raw = take(N * 2 * d * E);
+  for (PGradBufs& g : w.pg) {
+    g.gffn = take(N * d * E); g.dF = take(N * c.ffn * E); g.dX0 = take(N * d * E);
+    g.gop = take(N * ns * d * E); g.dQ = take(N * ns * d * E); g.gl2 = take(N * d * E);
+    g.dlogits = take(N * D->max_ld_logits() * E); g.draw = take(N * 2 * d * E);
+  }
   size_t dw = std::max<size_t>(2 * d * d, static_cast<size_t>(c.ffn) * d);
   dw = std::max(dw, d * ns * d);
   dw = std::max(dw, L * 2 * d * max_kdim);
@@ -108,7 +125,7 @@ struct Ctx {
   cudaStream_t st;
   int dt;
   const tnt_dropout_config* dr;     // this step's dropout (seed already advanced) or NULL
-  cudaStream_t side = nullptr;      // side stream of the parameter-gradient tails (NULL: everything on `st`)
+  cudaStream_t side = nullptr;      // parameter-gradient stream (NULL: everything on `st`)
   bool side_pending = false;        // work issued on `side` since the last join
   float* grad(const std::string& key) {
     auto it = D->grads.find(key);
@@ -120,17 +137,20 @@ struct Ctx {
   }
 };
 
-int gemm(Ctx& c, int layout, int epi, const void* A, long lda, const void* W, long ldw, void* C, long ldc, int M, int N,
-         int K, int dt_out, const void* res = nullptr, long ldr = 0, const int* m_dyn = nullptr, float alpha = 0.f,
-         const float* bias = nullptr, int groups = 1, long sa = 0, long sw = 0, long sr = 0, long sc = 0) {
+int gemm_on(cudaStream_t st, int dt_in, int layout, int epi, const void* A, long lda, const void* W, long ldw, void* C, long ldc,
+            int M, int N, int K, int dt_out, const void* res = nullptr, long ldr = 0, const int* m_dyn = nullptr, float alpha = 0.f,
+            const float* bias = nullptr, int groups = 1, long sa = 0, long sw = 0, long sr = 0, long sc = 0) {
   // (dropout never rides on a backward GEMM: masked gradients are materialised with dropout_apply)
   tnt_linear_params p = {};
   p.a = A; p.lda = lda; p.w = W; p.ldw = ldw; p.c = C; p.ldc = ldc; p.residual = res; p.ldr = ldr; p.bias = bias;
   p.M = M; p.N = N; p.K = K; p.m_dyn = m_dyn; p.groups = groups;
   p.stride_a = sa; p.stride_w = sw; p.stride_res = sr; p.stride_c = sc;
-  p.dtype_in = c.dt; p.dtype_out = dt_out; p.epilogue = epi; p.layout = layout; p.alpha = alpha;
-  return launch_gemm(&p, -1, nullptr, nullptr, c.st);
+  p.dtype_in = dt_in; p.dtype_out = dt_out; p.epilogue = epi; p.layout = layout; p.alpha = alpha;
+  return launch_gemm(&p, -1, nullptr, nullptr, st);
 }
+// data-gradient chain (the step's stream)
+template <typename... Args>
+int gemm(Ctx& c, Args... args) { return gemm_on(c.st, c.dt, args...); }
 
 int ln_bwd(Ctx& c, const void* x, long ldx, const void* dy, long lddy, void* dx, long lddx, const float* gamma,
            float* dgamma, float* dbeta, int rows, int C) {
@@ -142,9 +162,14 @@ int ln_bwd(Ctx& c, const void* x, long ldx, const void* dy, long lddy, void* dx,
   return tnt_layernorm_bwd(&p, c.st);
 }
 
-// Side stream protocol.  side_fork: everything issued on `st` so far is visible to the work that follows on `side`.
-// side_join: `st` waits for the side work -- REQUIRED before `st` overwrites a buffer a side kernel reads (w.dW before
-// the next weight-gradient GEMM, a dY buffer before its next writer) and before a stage event is recorded.
+// Parameter-gradient stream.  The backward's critical path is the DATA-gradient chain (dX flows from kernel to kernel,
+// every launch latency-bound at B*T = 2048 rows); the weight-gradient GEMMs, the weight-norm backward and the bias column
+// sums only consume what that chain produces.  They are issued on `side`, so they fill the SMs the chain leaves idle:
+//   side_fork  -- everything issued on `st` so far is visible to the work that follows on `side` (call it right after the
+//                 producer of a tensor the side work reads, before the next chain kernel is issued);
+//   side_join  -- `st` waits for all side work issued so far.
+// What the side work reads is never rewritten inside a layer (PGradBufs); the cross-layer reuse is ordered by
+// tnt_decoder::side_layer_done (layer_bwd).  w.dW / w.vecs are touched by side work only, so they are ordered in-stream.
 int side_fork(Ctx& c) {
   if (!c.side) return TNT_OK;
   TNT_CUDA(cudaEventRecord(c.D->side_fork, c.st));
@@ -159,32 +184,30 @@ int side_join(Ctx& c) {
   c.side_pending = false;
   return TNT_OK;
 }
-inline cudaStream_t side_or_main(Ctx& c) { return c.side ? c.side : c.st; }
+inline cudaStream_t pstream(Ctx& c) { return c.side ? c.side : c.st; }
+// weight-gradient GEMM (TN: reduction over the tokens) on the parameter-gradient stream
+template <typename... Args>
+int wgemm(Ctx& c, Args... args) { return gemm_on(pstream(c), c.dt, TNT_TN, EPI_NONE, args...); }
 
 // gradient of a GehringLinear: dWp [rows(prepared order), cols] fp32 -> weight_v / weight_g (or plain weight)
-// (side stream: the caller joins before dWp is overwritten)
 int linear_param_grads(Ctx& c, const std::string& prefix, const float* dWp, int rows, int cols, bool glu) {
   const float* g = c.raw(prefix + "weight_g");
   if (g) {
     const float* v = c.raw(prefix + "weight_v");
     float *dv = c.grad(prefix + "weight_v"), *dg = c.grad(prefix + "weight_g");
     TNT_CHECK_ARG(v && dv && dg, "train: '%sweight_v/_g' parameter or gradient buffer missing", prefix.c_str());
-    TNT_TRY(side_fork(c));
-    return wn_bwd(v, g, dWp, cols, dv, dg, rows, cols, glu, side_or_main(c));
+    return wn_bwd(v, g, dWp, cols, dv, dg, rows, cols, glu, pstream(c));
   }
   const float* v = c.raw(prefix + "weight");
   float* dv = c.grad(prefix + "weight");
   TNT_CHECK_ARG(v && dv, "train: '%sweight' parameter or gradient buffer missing", prefix.c_str());
-  TNT_TRY(side_fork(c));
-  return wn_bwd(v, nullptr, dWp, cols, dv, nullptr, rows, cols, glu, side_or_main(c));
+  return wn_bwd(v, nullptr, dWp, cols, dv, nullptr, rows, cols, glu, pstream(c));
 }
 
-// (side stream: the caller joins before dy is overwritten)
 int bias_grad(Ctx& c, const std::string& key, const void* dy, long ld, int M, int N, bool deinterleave, long offset = 0) {
   float* g = c.grad(key);
   TNT_CHECK_ARG(g, "train: gradient buffer for '%s' missing", key.c_str());
-  TNT_TRY(side_fork(c));
-  return colsum(dy, ld, M, N, nullptr, g + offset, c.dt, deinterleave, false, side_or_main(c));
+  return colsum(dy, ld, M, N, nullptr, g + offset, c.dt, deinterleave, false, pstream(c));
 }
 
 inline const char* off(const void* p, size_t elems, size_t E) { return static_cast<const char*>(p) + elems * E; }
@@ -233,14 +256,19 @@ tnt_xattn_params attn_params(const tnt_decoder* D, const tnt_contexts* ctx, cons
   return ap;
 }
 
+int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, int s);
+
 // ------------------------------------------------------------------------------ one layer, backward
 // in: gA = dL/dXout [N, d] (T x B order);  out: gA = dL/dXin
 // `dweights` (last layer only, copy heads): gradient w.r.t. the head-averaged attention weights the forward returned
+// Data-gradient chain on c.st; after each tensor a parameter gradient needs is produced, side_fork() and that parameter's
+// weight-gradient GEMM (+ weight-norm backward) and bias column sum go to the parameter-gradient stream.
 int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xin, const float* dweights = nullptr) {
   tnt_decoder* D = c.D;
   const tnt_decoder_config& cf = D->cfg;
   const LayerW& L = D->layers[l];
   const LayerAct& a = w.act[l];
+  const PGradBufs& G = w.pg[l & 1];
   const int d = cf.d, ns = cf.n_sources, B = ctx->B, T = ctx->T, N = B * T, H = cf.heads, dt = c.dt, ffn = cf.ffn;
   const int HK = H * L.K, ldl = D->ld_logits(L.K);
   const long nsd = static_cast<long>(ns) * d;
@@ -248,57 +276,60 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
   const std::string p = "layers." + std::to_string(l) + ".";
   const tnt_dropout_config* dr = c.dr;
   const float p_out = dr ? dr->dropout : 0.f;
+  // this layer rewrites the PGradBufs set layer l+2 used: its parameter-gradient work must have read them
+  if (c.side && l + 2 < cf.n_layers) TNT_CUDA(cudaStreamWaitEvent(c.st, D->side_layer_done[l + 2], 0));
   // ---- final LayerNorm and feed-forward: Xout = LN(yf), yf = drop(fc2(drop_relu(relu(fc1(X0))))) + X0
-  TNT_TRY(ln_bwd(c, a.yf, d, w.gA, d, w.gB, d, L.ln_f_g, c.grad(p + "final_layer_norm.weight"),
+  void* dyf = p_out > 0.f ? w.gB : G.gffn;        // gradient w.r.t. yf; G.gffn = the same with the fc2 dropout mask applied
+  TNT_TRY(ln_bwd(c, a.yf, d, w.gA, d, dyf, d, L.ln_f_g, c.grad(p + "final_layer_norm.weight"),
                  c.grad(p + "final_layer_norm.bias"), N, d));
-  const void* g_ffn = w.gB;                       // gradient w.r.t. the fc2 output (masked copy when dropout is on)
-  if (p_out > 0.f) {
-    TNT_TRY(dropout_apply(w.gB, d, nullptr, 0, w.gD, d, N, d, dt, drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_FFN_OUT)), c.st));
-    g_ffn = w.gD;
-  }
+  if (p_out > 0.f)
+    TNT_TRY(dropout_apply(dyf, d, nullptr, 0, G.gffn, d, N, d, dt, drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_FFN_OUT)), c.st));
+  TNT_TRY(side_fork(c));
+  TNT_TRY(wgemm(c, G.gffn, d, a.F, ffn, w.dW, ffn, d, ffn, N, TNT_F32));
+  TNT_TRY(linear_param_grads(c, p + "fc2.", w.dW, d, ffn, false));
+  TNT_TRY(bias_grad(c, p + "fc2.bias", G.gffn, d, N, d, false));
   // a.F holds the dropped-out ReLU output: F > 0 iff kept and active, and the kept elements carry 1 / (1 - p_relu)
   const float relu_scale = (dr && dr->relu_dropout > 0.f) ? 1.f / (1.f - dr->relu_dropout) : 0.f;
-  TNT_TRY(gemm(c, TNT_NN, EPI_RELU_BWD, g_ffn, d, L.wf2, ffn, w.dF, ffn, N, ffn, d, dt, a.F, ffn, nullptr, relu_scale));
-  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, g_ffn, d, a.F, ffn, w.dW, ffn, d, ffn, N, TNT_F32));
-  TNT_TRY(linear_param_grads(c, p + "fc2.", w.dW, d, ffn, false));
-  TNT_TRY(bias_grad(c, p + "fc2.bias", g_ffn, d, N, d, false));
-  TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.dF, ffn, L.wf1, d, w.gC, d, N, d, ffn, dt, w.gB, d));      // gC = dX0
-  TNT_TRY(side_join(c));                          // w.dW is rewritten
-  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.dF, ffn, a.X0, d, w.dW, d, ffn, d, N, TNT_F32));
+  TNT_TRY(gemm(c, TNT_NN, EPI_RELU_BWD, G.gffn, d, L.wf2, ffn, G.dF, ffn, N, ffn, d, dt, a.F, ffn, nullptr, relu_scale));
+  TNT_TRY(side_fork(c));
+  TNT_TRY(wgemm(c, G.dF, ffn, a.X0, d, w.dW, d, ffn, d, N, TNT_F32));
   TNT_TRY(linear_param_grads(c, p + "fc1.", w.dW, ffn, d, false));
-  TNT_TRY(bias_grad(c, p + "fc1.bias", w.dF, ffn, N, ffn, false));
+  TNT_TRY(bias_grad(c, p + "fc1.bias", G.dF, ffn, N, ffn, false));
+  TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, G.dF, ffn, L.wf1, d, G.dX0, d, N, d, ffn, dt, dyf, d));       // dX0
   // ---- context_fc over the concatenated, layer-normed per-source branches
-  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.gC, d, L.wc, nsd, w.dCAT, nsd, N, ns * d, d, dt));
-  TNT_TRY(side_join(c));                          // w.dW is rewritten
-  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.gC, d, a.CATln, nsd, w.dW, nsd, d, ns * d, N, TNT_F32));
+  TNT_TRY(side_fork(c));
+  TNT_TRY(wgemm(c, G.dX0, d, a.CATln, nsd, w.dW, nsd, d, ns * d, N, TNT_F32));
   TNT_TRY(linear_param_grads(c, p + "context_fc.", w.dW, d, ns * d, false));
-  TNT_TRY(bias_grad(c, p + "context_fc.bias", w.gC, d, N, d, false));
+  TNT_TRY(bias_grad(c, p + "context_fc.bias", G.dX0, d, N, d, false));
+  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, G.dX0, d, L.wc, nsd, w.dCAT, nsd, N, ns * d, d, dt));
+  void* dcatp = p_out > 0.f ? w.dCATp : G.gop;    // gradient w.r.t. CATpre; G.gop = the same with the out_proj dropout mask
   for (int s = 0; s < ns; ++s) {
     const std::string ln = p + "context_attn_lns." + cf.source_names[s] + ".";
     TNT_TRY(ln_bwd(c, off(a.CATpre, static_cast<size_t>(s) * d, E), nsd, off(w.dCAT, static_cast<size_t>(s) * d, E), nsd,
-                   off(w.dCATp, static_cast<size_t>(s) * d, E), nsd, L.ln_src_g + s * d, c.grad(ln + "weight"),
+                   off(dcatp, static_cast<size_t>(s) * d, E), nsd, L.ln_src_g + s * d, c.grad(ln + "weight"),
                    c.grad(ln + "bias"), N, d));
   }
   // ---- per-source attention branch: CATpre_s = drop(out_proj_s(attn_s)) + X1
-  const void* g_op = w.dCATp;                     // gradient w.r.t. the out_proj outputs [N, ns*d]
-  if (p_out > 0.f) {
-    TNT_TRY(dropout_apply(w.dCATp, nsd, nullptr, 0, w.dCAT, nsd, N, ns * d, dt,
+  if (p_out > 0.f)
+    TNT_TRY(dropout_apply(dcatp, nsd, nullptr, 0, G.gop, nsd, N, ns * d, dt,
                           drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_ATTN_OUT), nsd), c.st));
-    g_op = w.dCAT;
-  }
-  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, g_op, nsd, L.wo, d, w.dAO, nsd, N, d, d, dt, nullptr, 0, nullptr, 0.f, nullptr, ns,
-               d, static_cast<long>(d) * d, 0, d));
+  TNT_TRY(side_fork(c));
   for (int s = 0; s < ns; ++s) {
     const std::string at = p + "context_attns." + cf.source_names[s] + ".";
     float* dwo = c.grad(at + "out_proj.weight");
     TNT_CHECK_ARG(dwo, "train: gradient buffer for '%sout_proj.weight' missing", at.c_str());
-    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, off(g_op, static_cast<size_t>(s) * d, E), nsd, off(a.AO, static_cast<size_t>(s) * d, E),
-                 nsd, dwo, d, d, d, N, TNT_F32));
-    TNT_TRY(bias_grad(c, at + "out_proj.bias", off(g_op, static_cast<size_t>(s) * d, E), nsd, N, d, false));
+    TNT_TRY(wgemm(c, off(G.gop, static_cast<size_t>(s) * d, E), nsd, off(a.AO, static_cast<size_t>(s) * d, E), nsd, dwo, d, d, d, N,
+                  TNT_F32));
+    TNT_TRY(bias_grad(c, at + "out_proj.bias", off(G.gop, static_cast<size_t>(s) * d, E), nsd, N, d, false));
+  }
+  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, G.gop, nsd, L.wo, d, w.dAO, nsd, N, d, d, dt, nullptr, 0, nullptr, 0.f, nullptr, ns,
+               d, static_cast<long>(d) * d, 0, d));
+  for (int s = 0; s < ns; ++s) {
+    const std::string at = p + "context_attns." + cf.source_names[s] + ".";
     XattnBwd xb;
     xb.f = attn_params(D, ctx, w, l, s, dr);
     xb.dout = off(w.dAO, static_cast<size_t>(s) * d, E);
-    xb.dq = off(w.dQ, static_cast<size_t>(s) * d, E);
+    xb.dq = off(G.dQ, static_cast<size_t>(s) * d, E);
     xb.dk = off(w.dkv[s], static_cast<size_t>(l) * 2 * d, E);
     xb.dv = off(xb.dk, d, E);
     xb.scratch = w.attn_scr;
@@ -308,59 +339,61 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
     float* dwq = c.grad(at + "in_proj_weight");
     if (!dwq) dwq = c.grad(at + "q_proj_weight");
     TNT_CHECK_ARG(dwq, "train: gradient buffer for the query projection of '%s' missing", at.c_str());
-    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, off(w.dQ, static_cast<size_t>(s) * d, E), nsd, a.X1, d, dwq, d, d, d, N, TNT_F32));
-    TNT_TRY(bias_grad(c, at + "in_proj_bias", off(w.dQ, static_cast<size_t>(s) * d, E), nsd, N, d, false));
+    TNT_TRY(side_fork(c));
+    TNT_TRY(wgemm(c, off(G.dQ, static_cast<size_t>(s) * d, E), nsd, a.X1, d, dwq, d, d, d, N, TNT_F32));
+    TNT_TRY(bias_grad(c, at + "in_proj_bias", off(G.dQ, static_cast<size_t>(s) * d, E), nsd, N, d, false));
+    // K/V projection parameters of this layer and source: dkv's columns of layer l are final
+    TNT_TRY(kv_param_grads(c, ctx, w, l, s));
   }
   // dX1 = dQ . Wq + sum_s dCATpre_s
-  TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.dQ, nsd, L.wq, d, w.gD, d, N, d, ns * d, dt, w.dCATp, nsd));
-  TNT_TRY(add_col_blocks(w.gD, d, w.dCATp, nsd, N, d, 1, ns, dt, c.st));
+  TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, G.dQ, nsd, L.wq, d, w.gD, d, N, d, ns * d, dt, dcatp, nsd));
+  TNT_TRY(add_col_blocks(w.gD, d, dcatp, nsd, N, d, 1, ns, dt, c.st));
   // ---- conv block: X1 = LN(yc), yc = linear2(conv(h)) + Xin, h = GLU(linear1(Xin))
-  TNT_TRY(ln_bwd(c, a.yc, d, w.gD, d, w.gB, d, L.ln_conv_g, c.grad(p + "conv_layer_norm.weight"),
-                 c.grad(p + "conv_layer_norm.bias"), N, d));                                          // gB = dyc
-  const void* g_l2 = w.gB;                        // gradient w.r.t. the linear2 output (masked copy when dropout is on)
-  if (p_out > 0.f) {
-    TNT_TRY(dropout_apply(w.gB, d, nullptr, 0, w.gA, d, N, d, dt, drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_CONV_OUT)), c.st));
-    g_l2 = w.gA;
-  }
-  TNT_TRY(side_join(c));                          // w.gC (read by the context_fc bias sum) and w.dW are rewritten
-  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, g_l2, d, L.w2, d, w.gC, d, N, d, d, dt));                         // gC = dcbuf
-  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, g_l2, d, a.cbuf, d, w.dW, d, d, d, N, TNT_F32));
+  void* dyc = p_out > 0.f ? w.gB : G.gl2;         // gradient w.r.t. yc; G.gl2 = the same with the linear2 dropout mask
+  TNT_TRY(ln_bwd(c, a.yc, d, w.gD, d, dyc, d, L.ln_conv_g, c.grad(p + "conv_layer_norm.weight"),
+                 c.grad(p + "conv_layer_norm.bias"), N, d));
+  if (p_out > 0.f)
+    TNT_TRY(dropout_apply(dyc, d, nullptr, 0, G.gl2, d, N, d, dt, drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_CONV_OUT)), c.st));
+  TNT_TRY(side_fork(c));
+  TNT_TRY(wgemm(c, G.gl2, d, a.cbuf, d, w.dW, d, d, d, N, TNT_F32));
   TNT_TRY(linear_param_grads(c, p + "linear2.", w.dW, d, d, false));
-  TNT_TRY(bias_grad(c, p + "linear2.bias", g_l2, d, N, d, false));
+  TNT_TRY(bias_grad(c, p + "linear2.bias", G.gl2, d, N, d, false));
+  TNT_TRY(gemm(c, TNT_NN, EPI_NONE, G.gl2, d, L.w2, d, w.gC, d, N, d, d, dt));                        // gC = dcbuf
   {
     tnt_dynconv_bwd_params bp = {};
     bp.x = a.h; bp.ldx = d; bp.logits = a.logits; bp.ldl = ldl; bp.dy = w.gC; bp.lddy = d; bp.dx = w.gD; bp.lddx = d;
-    bp.dlogits = w.dlogits; bp.lddl = ldl; bp.T = T; bp.B = B; bp.C = d; bp.H = H; bp.K = L.K; bp.dtype = dt;
+    bp.dlogits = G.dlogits; bp.lddl = ldl; bp.T = T; bp.B = B; bp.C = d; bp.H = H; bp.K = L.K; bp.dtype = dt;
     bp.drop = drop_site(dr, dr ? dr->weight_dropout : 0.f, TNT_DROP_SITE(l, TNT_DROP_TAPS));
     TNT_TRY(tnt_dynconv_bwd(&bp, c.st));                                                             // gD = dh (value path)
   }
   {
     float* dwt = c.grad(p + "conv.weight_linear.weight");
     TNT_CHECK_ARG(dwt, "train: gradient buffer for '%sconv.weight_linear.weight' missing", p.c_str());
-    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.dlogits, ldl, a.h, d, dwt, d, HK, d, N, TNT_F32));
+    TNT_TRY(side_fork(c));
+    TNT_TRY(wgemm(c, G.dlogits, ldl, a.h, d, dwt, d, HK, d, N, TNT_F32));
   }
-  TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.dlogits, ldl, L.wtap, d, w.gC, d, N, d, HK, dt, w.gD, d));   // gC = dh
+  TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, G.dlogits, ldl, L.wtap, d, w.gC, d, N, d, HK, dt, w.gD, d));   // gC = dh
   const bool in_drop = dr && dr->input_dropout > 0.f;
   const void* X1in = in_drop ? a.Xd : Xin;        // what linear1 read in the forward
   TNT_TRY(gemm(c, TNT_NT, EPI_NONE, X1in, d, L.w1, d, w.raw, 2 * d, N, 2 * d, d, dt, nullptr, 0, nullptr, 0.f, L.b1));
-  TNT_TRY(glu_bwd(w.raw, 2 * d, w.gC, d, w.draw, 2 * d, N, d, dt, c.st));
-  TNT_TRY(side_join(c));                          // w.gA (the masked linear2 gradient the bias sum reads) and w.dW are rewritten
-  if (in_drop) {                                  // gA = dXin = drop(draw . W1) + dyc
-    TNT_TRY(gemm(c, TNT_NN, EPI_NONE, w.draw, 2 * d, L.w1, d, w.gC, d, N, d, 2 * d, dt));
-    TNT_TRY(dropout_apply(w.gC, d, w.gB, d, w.gA, d, N, d, dt, drop_site(dr, dr->input_dropout, TNT_DROP_SITE(l, TNT_DROP_INPUT)), c.st));
-  } else {
-    TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, w.draw, 2 * d, L.w1, d, w.gA, d, N, d, 2 * d, dt, w.gB, d));    // gA = dXin
-  }
-  TNT_TRY(gemm(c, TNT_TN, EPI_NONE, w.draw, 2 * d, X1in, d, w.dW, d, 2 * d, d, N, TNT_F32));
+  TNT_TRY(glu_bwd(w.raw, 2 * d, w.gC, d, G.draw, 2 * d, N, d, dt, c.st));
+  TNT_TRY(side_fork(c));
+  TNT_TRY(wgemm(c, G.draw, 2 * d, X1in, d, w.dW, d, 2 * d, d, N, TNT_F32));
   TNT_TRY(linear_param_grads(c, p + "linear1.", w.dW, 2 * d, d, true));
-  TNT_TRY(bias_grad(c, p + "linear1.bias", w.draw, 2 * d, N, 2 * d, true));
+  TNT_TRY(bias_grad(c, p + "linear1.bias", G.draw, 2 * d, N, 2 * d, true));
+  if (in_drop) {                                  // gA = dXin = drop(draw . W1) + dyc
+    TNT_TRY(gemm(c, TNT_NN, EPI_NONE, G.draw, 2 * d, L.w1, d, w.gC, d, N, d, 2 * d, dt));
+    TNT_TRY(dropout_apply(w.gC, d, dyc, d, w.gA, d, N, d, dt, drop_site(dr, dr->input_dropout, TNT_DROP_SITE(l, TNT_DROP_INPUT)), c.st));
+  } else {
+    TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, G.draw, 2 * d, L.w1, d, w.gA, d, N, d, 2 * d, dt, dyc, d));    // gA = dXin
+  }
   return TNT_OK;
 }
 
 
 // ------------------------------------------------------------------------------ K/V projection parameters
-// of layer l, source s (k/v_proj_weight or in_proj_weight rows [d, 3d), in_proj_bias[d:], bias_k, bias_v): computed
-// right after the layer's backward so its gradients are final with the layer's stage.
+// of layer l, source s (k/v_proj_weight or in_proj_weight rows [d, 3d), in_proj_bias[d:], bias_k, bias_v): issued on the
+// parameter-gradient stream as soon as the layer's attention backward has written dkv's columns of layer l.
 int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, int s) {
   tnt_decoder* D = c.D;
   const tnt_decoder_config& cf = D->cfg;
@@ -371,10 +404,8 @@ int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, int s) {
   const void* dkv = off(w.dkv[s], static_cast<size_t>(l) * 2 * d, E);     // columns [K | V] of this layer
   float *gk = c.grad(at + "bias_k"), *gv = c.grad(at + "bias_v"), *gb = c.grad(at + "in_proj_bias");
   TNT_CHECK_ARG(gk && gv && gb, "train: gradient buffer for '%sbias_k / bias_v / in_proj_bias' missing", at.c_str());
-  TNT_TRY(side_join(c));                          // w.dW is rewritten below (and w.vecs by the side work of this call)
-  // the extra-row gradients and the bias column sum stream dkv from HBM beside the (tensor-bound) weight-gradient GEMM
   TNT_TRY(side_fork(c));
-  cudaStream_t ss = side_or_main(c);
+  cudaStream_t ss = pstream(c);
   TNT_TRY(kv_extra_grad(dkv, ldkv, S, B, 2 * d, w.vecs, c.dt, ss));        // the learned extra key row (index S)
   TNT_CUDA(cudaMemcpyAsync(gk, w.vecs, sizeof(float) * d, cudaMemcpyDeviceToDevice, ss));
   TNT_CUDA(cudaMemcpyAsync(gv, w.vecs + d, sizeof(float) * d, cudaMemcpyDeviceToDevice, ss));
@@ -394,19 +425,19 @@ int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, int s) {
   }
   if (G > 1) {
     float* parts = w.dW + (gi ? 0 : static_cast<size_t>(2) * d * kd);
-    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, dkv, ldkv, ctx->memory[s], kd, parts, kd, 2 * d, kd, Kr / G, TNT_F32, nullptr, 0, nullptr, 0.f,
-                 nullptr, G, static_cast<long>(Kr / G) * ldkv, static_cast<long>(Kr / G) * kd, 0, static_cast<long>(2) * d * kd));
-    TNT_TRY(sum_partials(dst, parts, G, static_cast<long>(2) * d * kd, c.st));
+    TNT_TRY(wgemm(c, dkv, ldkv, ctx->memory[s], kd, parts, kd, 2 * d, kd, Kr / G, TNT_F32, nullptr, 0, nullptr, 0.f,
+                  nullptr, G, static_cast<long>(Kr / G) * ldkv, static_cast<long>(Kr / G) * kd, 0, static_cast<long>(2) * d * kd));
+    TNT_TRY(sum_partials(dst, parts, G, static_cast<long>(2) * d * kd, ss));
   } else if (S * B > 0) {
-    TNT_TRY(gemm(c, TNT_TN, EPI_NONE, dkv, ldkv, ctx->memory[s], kd, dst, kd, 2 * d, kd, S * B, TNT_F32));
+    TNT_TRY(wgemm(c, dkv, ldkv, ctx->memory[s], kd, dst, kd, 2 * d, kd, S * B, TNT_F32));
   } else {
-    TNT_CUDA(cudaMemsetAsync(dst, 0, sizeof(float) * 2 * d * kd, c.st));
+    TNT_CUDA(cudaMemsetAsync(dst, 0, sizeof(float) * 2 * d * kd, ss));
   }
   if (!gi) {
     float *gwk = c.grad(at + "k_proj_weight"), *gwv = c.grad(at + "v_proj_weight");
     TNT_CHECK_ARG(gwk && gwv, "train: gradient buffer for '%sk/v_proj_weight' missing", at.c_str());
-    TNT_CUDA(cudaMemcpyAsync(gwk, w.dW, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, c.st));
-    TNT_CUDA(cudaMemcpyAsync(gwv, w.dW + static_cast<size_t>(d) * kd, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, c.st));
+    TNT_CUDA(cudaMemcpyAsync(gwk, w.dW, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, ss));
+    TNT_CUDA(cudaMemcpyAsync(gwv, w.dW + static_cast<size_t>(d) * kd, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, ss));
   }
   return TNT_OK;
 }
@@ -516,7 +547,10 @@ int step_setup(tnt_decoder* D, const tnt_contexts* ctx, void* workspace, size_t 
   if (use_side && !D->side_stream) {
     int lo = 0, hi = 0;
     TNT_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-    TNT_CUDA(cudaStreamCreateWithPriority(&D->side_stream, cudaStreamNonBlocking, hi));
+    // measured (B = 64, one GPU): highest priority 7.05 ms per step, lowest 7.12 ms -- the parameter-gradient kernels are
+    // short, and letting them in first keeps them from lingering beside three or four chain kernels (TNT_SIDE_PRIO=lo: A/B)
+    const char* pe = getenv("TNT_SIDE_PRIO");
+    TNT_CUDA(cudaStreamCreateWithPriority(&D->side_stream, cudaStreamNonBlocking, (pe && pe[0] == 'l') ? lo : hi));
     TNT_CUDA(cudaEventCreateWithFlags(&D->side_fork, cudaEventDisableTiming));
     TNT_CUDA(cudaEventCreateWithFlags(&D->side_join, cudaEventDisableTiming));
   }
@@ -524,6 +558,11 @@ int step_setup(tnt_decoder* D, const tnt_contexts* ctx, void* workspace, size_t 
     cudaEvent_t e;
     TNT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     D->stage_events.push_back(e);
+  }
+  while (static_cast<int>(D->side_layer_done.size()) < Ls) {
+    cudaEvent_t e;
+    TNT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    D->side_layer_done.push_back(e);
   }
   return TNT_OK;
 }
@@ -586,9 +625,15 @@ int train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, co
   for (int l = Ls - 1; l >= 0; --l) {
     const void* xin = l == 0 ? w.emb : w.act[l - 1].Xout;
     TNT_TRY(layer_bwd(c, ctx, w, l, xin, (ext && l == Ls - 1) ? ext->dattn : nullptr));
-    for (int s = 0; s < ns; ++s) TNT_TRY(kv_param_grads(c, ctx, w, l, s));
-    TNT_TRY(side_join(c));
-    TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], st));
+    // stage Ls - l is final when the chain AND the parameter-gradient work of layer l are: the event is recorded on the
+    // parameter-gradient stream after it has caught up with the chain (the chain itself does not wait)
+    if (c.side) {
+      TNT_TRY(side_fork(c));
+      TNT_CUDA(cudaEventRecord(D->side_layer_done[l], c.side));
+      TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], c.side));
+    } else {
+      TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], st));
+    }
   }
   const tnt_dropout d_emb = drop_site(dr, dr ? dr->dropout : 0.f, TNT_DROP_SITE_EMBED);
   if (d_emb.p > 0.f) TNT_TRY(dropout_apply(w.gA, d, nullptr, 0, w.gA, d, N, d, cf.dtype, d_emb, st));
@@ -597,6 +642,7 @@ int train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, co
     TNT_TRY(add_col_blocks(w.gA, d, w.gB, d, N, d, 0, 1, cf.dtype, st));
   }
   TNT_TRY(embed_bwd(c, ids, B, T, w, w.gA));
+  TNT_TRY(side_join(c));                         // the caller's stream has every gradient from here on
   TNT_CUDA(cudaEventRecord(D->stage_events[Ls + 1], st));
   return TNT_OK;
 }

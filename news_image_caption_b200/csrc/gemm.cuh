@@ -102,9 +102,20 @@ __device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m
   }
   if (EPI == EPI_RELU_BWD) {
     const TOut* rrow = reinterpret_cast<const TOut*>(g.res) + grp * g.sres + static_cast<long>(m) * g.ldr;
+    if (NC % 8 == 0 && g.vec_ok && n0 + NC <= g.N) {       // 16-byte loads of the saved activation (scalar loads: 32 sectors
+#pragma unroll                                             // per instruction and warp -- the epilogue was 3x the k-loop)
+      for (int i = 0; i < NC; i += 8) {
+        float t[8];
+        load8(rrow + n0 + i, t);
 #pragma unroll
-    for (int i = 0; i < NC; ++i)
-      if (n0 + i < g.N && !(to_f(rrow[n0 + i]) > 0.f)) acc[i] = 0.f;
+        for (int j = 0; j < 8; ++j)
+          if (!(t[j] > 0.f)) acc[i + j] = 0.f;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < NC; ++i)
+        if (n0 + i < g.N && !(to_f(rrow[n0 + i]) > 0.f)) acc[i] = 0.f;
+    }
   }
   if (EPI == EPI_RESIDUAL) {
     if (g.drop.thr) {
