@@ -18,7 +18,13 @@ namespace tnt {
 namespace {
 
 constexpr int kHeadsPerCta = 8;
-constexpr int kWarps = 4;
+// 8 warps x kUnroll keys in flight per item: the launch lasts as long as its longest item (an article of ~514 live keys is a
+// serial chain of n_live / (kWarps * kUnroll) load round trips).  Measured on the B = 256 generation: 4 warps 24.75 ms
+// (4.83 TB/s in the attention launches), 8 warps 24.19 ms (5.22 TB/s), 16 warps 26.67 ms (4.14 TB/s: too few CTAs per SM).
+#ifndef TNT_STEP_WARPS
+#define TNT_STEP_WARPS 8
+#endif
+constexpr int kWarps = TNT_STEP_WARPS;
 constexpr int kUnroll = 4;
 constexpr int kMaxKeys = 2048;
 

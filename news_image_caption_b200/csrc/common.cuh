@@ -114,6 +114,12 @@ struct PerDeviceOnce {          // `static PerDeviceOnce once; if (once.first())
     return true;
   }
 };
+// SM budget of the launches the calling thread issues (0 = all): sub-batch chains that run side by side on several streams
+// size their grids for a share of the GPU, so that their CTAs can be resident at the same time (engine.cuh, SubBatches)
+inline int& sm_budget() {
+  static thread_local int b = 0;
+  return b;
+}
 inline int num_sms() {
   static int n[kMaxDevices] = {};
   const int dev = cur_device();
@@ -121,8 +127,14 @@ inline int num_sms() {
     cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev);
     if (n[dev] <= 0) n[dev] = 148;
   }
-  return n[dev];
+  const int b = sm_budget();
+  return b > 0 && b < n[dev] ? b : n[dev];
 }
+struct SmBudget {                // RAII: SmBudget guard(n) -- launches issued while it lives see n SMs
+  int keep;
+  explicit SmBudget(int n) : keep(sm_budget()) { sm_budget() = n; }
+  ~SmBudget() { sm_budget() = keep; }
+};
 inline cudaStream_t as_stream(tnt_stream s) { return reinterpret_cast<cudaStream_t>(s); }
 
 // ------------------------------------------------------------------ counter-based dropout (tnt_dropout)

@@ -60,11 +60,19 @@ struct tnt_decoder {
   void* emb_proj[TNT_MAX_CLUSTERS] = {};   // band projections [d, dim_i] in the engine dtype (training backward)
   int emb_dim[TNT_MAX_CLUSTERS] = {};
   std::vector<cudaEvent_t> stage_events;   // training: gradients of stage i are final (tnt_decoder_stream_wait_stage)
-  // training backward: every parameter gradient (weight-gradient GEMM, weight-norm backward, bias column sum) runs on a
-  // side stream beside the latency-bound data-gradient chain (engine_train.cu)
-  cudaStream_t side_stream = nullptr;
-  cudaEvent_t side_fork = nullptr, side_join = nullptr;
-  std::vector<cudaEvent_t> side_layer_done;   // the parameter-gradient work of layer l has been issued up to here
+  // training backward: every parameter gradient (weight-gradient GEMM, weight-norm backward, bias column sum) runs on one
+  // of a few side streams beside the latency-bound data-gradient chain (engine_train.cu)
+  static constexpr int kSideStreams = 4;
+  int n_side = 0;                                  // side streams in use (0: everything on the step's stream)
+  cudaStream_t side_streams[kSideStreams] = {};
+  cudaStream_t stage_stream = nullptr;             // carries no kernels: joins chain + side streams for the stage events
+  cudaEvent_t side_fork = nullptr, side_join[kSideStreams] = {};
+  std::vector<cudaEvent_t> side_layer_done;        // [layer * kSideStreams + k]: side stream k has issued layer l's work
+  // inference: the batch is cut into a few sub-batches whose latency-bound kernel chains run side by side on these streams
+  // (engine_fwd.cu: SubBatches)
+  static constexpr int kMaxSub = 4;
+  cudaStream_t sub_streams[kMaxSub - 1] = {};
+  cudaEvent_t sub_fork = nullptr, sub_join[kMaxSub - 1] = {};
   std::map<std::string, float*> grads; // training: fp32 gradient buffer per state_dict key (tnt_decoder_set_grad)
   // data-parallel training: embedding-row gradients go to a packed list instead of the dense band tables
   void* sparse_rows = nullptr; long long* sparse_meta = nullptr; int* sparse_count = nullptr; int sparse_capacity = 0;
@@ -104,13 +112,34 @@ struct FwdWs {
   int* sched;                    // 2 zeroed ints: dynamic work counters of the decode-step attention (or NULL)
   float* step_scores = nullptr;  // generation through the copy head: [B, H, S_w + 2] score dump of the decode-step attention
   float* step_lse = nullptr;     //   and its [B, H] log-sum-exp
+  int kv_B = 0;                  // context entries the K/V buffers hold when the rows are a SUB-batch of them (0: B / kv_group)
   size_t total;
 };
+// Sub-batches.  At the benchmark's batch sizes every kernel of a decoder layer is latency-bound (a 2048-row GEMM is one wave
+// of tiles, most of its 12 us is launch, pipeline fill and epilogue), and the decode step alternates between one HBM-bound
+// kernel (attention over the K/V cache) and ~60 such launches.  The captions are independent, so the batch is cut into
+// n row ranges; each runs the same kernel chain on its own stream (sub-batch 0 on the caller's), and one range's
+// latency hides behind another's work.  The K/V projections are still ONE GEMM per source over the whole batch.
+struct SubBatches {
+  int n = 1;
+  int b0[tnt_decoder::kMaxSub + 1] = {0};          // sub-batch i = context entries [b0[i], b0[i+1])
+  cudaStream_t st[tnt_decoder::kMaxSub] = {};
+};
+// plan: env TNT_SUB_BATCHES (default `dflt`), at least `min_rows` captions per sub-batch; creates the streams on first use
+int sub_plan(tnt_decoder* d, int B, int dflt, int min_rows, cudaStream_t st, SubBatches* sb);
+int sub_fork(tnt_decoder* d, const SubBatches& sb);      // streams 1.. see what has been issued on stream 0
+int sub_join(tnt_decoder* d, const SubBatches& sb);      // stream 0 waits for streams 1..
+// workspace / contexts of sub-batch i: rows [b0*T, b1*T) of every activation buffer (a private [T, nb, .] block), the K/V
+// cache entries b0.. of the SHARED cache (kv_B = B), the slices of the masks / live-tile words / orders
+FwdWs sub_ws(const tnt_decoder* d, const FwdWs& w, const SubBatches& sb, int i, int B, int T, const int* S);
+tnt_contexts sub_ctx(const tnt_contexts& c, const SubBatches& sb, int i);
 // B_kv >= 0: number of context entries the K/V cache holds when it differs from the row batch B (beam search)
 FwdWs carve_fwd(const tnt_decoder* d, int B, int T, const int* S, void* ws, bool with_kv, int B_kv = -1);
 
 int embed(tnt_decoder* d, const int64_t* ids, int B, int T, void* out, const int* start_pos, cudaStream_t st);
-int project_kv(tnt_decoder* d, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st, bool decode_order = false);
+struct SubBatches;
+int project_kv(tnt_decoder* d, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st, bool decode_order = false,
+               const SubBatches* sb = nullptr);
 // caller-owned chronological conv history of one layer (the reference's `DynamicConv1dTBC.<id>.input_buffer`,
 // dynamic.py:95-99): `in` = the last `len` (<= K-1) conv inputs [len, B, C], oldest first; `out` (optional, must not
 // alias `in`) receives the last min(K-1, len + T) rows of [in ; this call's conv inputs]

@@ -80,7 +80,7 @@ FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool
   w.CATln = w.CAT;
   for (size_t s = 0; s < ns; ++s)
     w.kv[s] = with_kv ? take(static_cast<size_t>(S[s] + 2) * (B_kv >= 0 ? B_kv : B) * c.n_layers * 2 * d * E) : nullptr;
-  w.sched = with_kv ? static_cast<int*>(take(2 * sizeof(int))) : nullptr;    // work counters of the decode-step attention
+  w.sched = with_kv ? static_cast<int*>(take(2 * tnt_decoder::kMaxSub * sizeof(int))) : nullptr;    // work counters of the decode-step attention (a pair per sub-batch)
   for (size_t s = 0; s < ns; ++s) w.order[s] = with_kv ? static_cast<int*>(take(sizeof(int) * (B_kv >= 0 ? B_kv : B))) : nullptr;
   for (size_t s = 0; s < ns; ++s)
     w.tile_live[s] = with_kv ? static_cast<uint32_t*>(take(sizeof(uint32_t) * (B_kv >= 0 ? B_kv : B))) : nullptr;
@@ -88,13 +88,84 @@ FwdWs carve_fwd(const tnt_decoder* D, int B, int T, const int* S, void* ws, bool
   return w;
 }
 
+static int g_sub_batches = 0;    // test hook (tnt_debug_sub_batches): > 0 overrides TNT_SUB_BATCHES / the default
+
+int sub_plan(tnt_decoder* D, int B, int dflt, int min_rows, cudaStream_t st, SubBatches* sb) {
+  static const int env_n = [] { const char* e = getenv("TNT_SUB_BATCHES"); return e ? atoi(e) : -1; }();
+  int n = g_sub_batches > 0 ? g_sub_batches : env_n >= 1 ? env_n : dflt;
+  if (g_sub_batches > 0) min_rows = 1;
+  n = std::max(1, std::min(n, static_cast<int>(tnt_decoder::kMaxSub)));
+  while (n > 1 && B / n < min_rows) --n;
+  sb->n = n;
+  for (int i = 0; i <= n; ++i) sb->b0[i] = static_cast<int>(static_cast<long>(B) * i / n);
+  sb->st[0] = st;
+  if (n > 1 && !D->sub_fork) {
+    TNT_CUDA(cudaEventCreateWithFlags(&D->sub_fork, cudaEventDisableTiming));
+    for (int i = 0; i < tnt_decoder::kMaxSub - 1; ++i) {
+      TNT_CUDA(cudaStreamCreateWithFlags(&D->sub_streams[i], cudaStreamNonBlocking));
+      TNT_CUDA(cudaEventCreateWithFlags(&D->sub_join[i], cudaEventDisableTiming));
+    }
+  }
+  for (int i = 1; i < n; ++i) sb->st[i] = D->sub_streams[i - 1];
+  return TNT_OK;
+}
+
+int sub_fork(tnt_decoder* D, const SubBatches& sb) {
+  if (sb.n <= 1) return TNT_OK;
+  TNT_CUDA(cudaEventRecord(D->sub_fork, sb.st[0]));
+  for (int i = 1; i < sb.n; ++i) TNT_CUDA(cudaStreamWaitEvent(sb.st[i], D->sub_fork, 0));
+  return TNT_OK;
+}
+
+int sub_join(tnt_decoder* D, const SubBatches& sb) {
+  for (int i = 1; i < sb.n; ++i) {
+    TNT_CUDA(cudaEventRecord(D->sub_join[i - 1], sb.st[i]));
+    TNT_CUDA(cudaStreamWaitEvent(sb.st[0], D->sub_join[i - 1], 0));
+  }
+  return TNT_OK;
+}
+
+FwdWs sub_ws(const tnt_decoder* D, const FwdWs& w, const SubBatches& sb, int i, int B, int T, const int* S) {
+  (void)S;
+  const tnt_decoder_config& c = D->cfg;
+  const size_t E = D->esz(), r0 = static_cast<size_t>(sb.b0[i]) * T, d = c.d, ns = c.n_sources;
+  auto rows = [&](void* p, size_t width) -> void* { return p ? static_cast<char*>(p) + r0 * width * E : nullptr; };
+  FwdWs f = w;
+  f.X0 = rows(w.X0, d); f.X1 = rows(w.X1, d); f.h = rows(w.h, d);
+  f.logits = rows(w.logits, D->max_ld_logits());
+  f.cbuf = rows(w.cbuf, d); f.ybuf = rows(w.ybuf, d);
+  f.Q = rows(w.Q, ns * d); f.AO = rows(w.AO, ns * d); f.CAT = rows(w.CAT, ns * d);
+  f.F = rows(w.F, c.ffn);
+  f.ybuf2 = f.ybuf;
+  f.CATln = f.CAT;
+  f.Xd = nullptr;
+  const size_t ldkv = static_cast<size_t>(c.n_layers) * 2 * d;
+  for (size_t s = 0; s < ns; ++s) {
+    f.kv[s] = w.kv[s] ? static_cast<char*>(w.kv[s]) + static_cast<size_t>(sb.b0[i]) * ldkv * E : nullptr;
+    f.lse[s] = nullptr;
+    f.tile_live[s] = w.tile_live[s] ? w.tile_live[s] + sb.b0[i] : nullptr;
+    f.order[s] = w.order[s] ? w.order[s] + sb.b0[i] : nullptr;
+  }
+  f.sched = w.sched ? w.sched + 2 * i : nullptr;
+  f.kv_B = B;
+  return f;
+}
+
+tnt_contexts sub_ctx(const tnt_contexts& c, const SubBatches& sb, int i) {
+  tnt_contexts s = c;
+  s.B = sb.b0[i + 1] - sb.b0[i];
+  for (int k = 0; k < TNT_MAX_SOURCES; ++k)
+    if (c.pad_mask[k]) s.pad_mask[k] = c.pad_mask[k] + static_cast<size_t>(sb.b0[i]) * c.S[k];
+  return s;
+}
+
 // K/V of every layer for every source in ONE GEMM per source: [S*B, kdim] x [L*2d, kdim]^T (+bias).
 // The reference recomputes these projections in every layer call and every decoding step
 // (multi_head.py:347-352 with incremental_state=None, decoder_flattened.py:305,323); same numbers.
-int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st, bool decode_order) {
+int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t st, bool decode_order, const SubBatches* sb) {
   const tnt_decoder_config& c = D->cfg;
   const int ldkv = c.n_layers * 2 * c.d;
-  if (w.sched) TNT_CUDA(cudaMemsetAsync(w.sched, 0, 2 * sizeof(int), st));   // every launch leaves them at zero again
+  if (w.sched) TNT_CUDA(cudaMemsetAsync(w.sched, 0, 2 * tnt_decoder::kMaxSub * sizeof(int), st));   // every launch leaves them at zero again
   for (int s = 0; s < c.n_sources; ++s) {
     const int grid = std::min<long>((static_cast<long>(ctx->B) * ldkv + 255) / 256, 4L * num_sms());
     const bool scan = w.tile_live[s] && ctx->pad_mask[s] && ctx->S[s] > 0;
@@ -107,7 +178,14 @@ int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStre
                                                                 grid, ctx->pad_mask[s], w.tile_live[s]);
     TNT_LAUNCHED();
     // generation: the decode-step attention starts the captions with the most live keys first (once per call)
-    if (decode_order && scan && w.order[s] && ctx->B <= 4096) TNT_TRY(xattn_live_order(w.tile_live[s], ctx->B, w.order[s], st));
+    if (decode_order && scan && w.order[s] && ctx->B <= 4096) {
+      if (sb && sb->n > 1) {                 // an order per sub-batch, relative to its first entry
+        for (int i = 0; i < sb->n; ++i)
+          TNT_TRY(xattn_live_order(w.tile_live[s] + sb->b0[i], sb->b0[i + 1] - sb->b0[i], w.order[s] + sb->b0[i], st));
+      } else {
+        TNT_TRY(xattn_live_order(w.tile_live[s], ctx->B, w.order[s], st));
+      }
+    }
     if (ctx->S[s] == 0) continue;
     TNT_CHECK_ARG(ctx->memory[s], "decoder: context '%s' missing", c.source_names[s]);
     char pname[40];
@@ -189,7 +267,7 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
     ap.q = static_cast<const char*>(w.Q) + static_cast<size_t>(s) * d * E;
     ap.q_stride_t = static_cast<long>(B) * ns * d; ap.q_stride_b = static_cast<long>(ns) * d;
     ap.k = static_cast<const char*>(w.kv[s]) + static_cast<size_t>(l) * 2 * d * E;
-    ap.k_stride_s = static_cast<long>(B / (kv_group > 1 ? kv_group : 1)) * ldkv; ap.k_stride_b = ldkv;   // cache rows = context entries
+    ap.k_stride_s = static_cast<long>(w.kv_B ? w.kv_B : B / (kv_group > 1 ? kv_group : 1)) * ldkv; ap.k_stride_b = ldkv;   // cache rows = context entries
     ap.v = static_cast<const char*>(ap.k) + static_cast<size_t>(d) * E;
     ap.v_stride_s = ap.k_stride_s; ap.v_stride_b = ap.k_stride_b;
     ap.out = static_cast<char*>(w.AO) + static_cast<size_t>(s) * d * E;
@@ -263,6 +341,8 @@ int embed(tnt_decoder* D, const int64_t* ids, int B, int T, void* out, const int
 
 using namespace tnt;
 
+extern "C" void tnt_debug_sub_batches(int n) { tnt::g_sub_batches = n > 0 ? n : 0; }
+
 extern "C" size_t tnt_decoder_workspace_bytes(const tnt_decoder* d, int B, int T, const int* S) {
   if (!d || !S) return 0;
   return carve_fwd(d, B, T, S, nullptr, true).total;
@@ -283,18 +363,33 @@ extern "C" int tnt_decoder_forward(tnt_decoder* D, const int64_t* ids, const tnt
   }
   cudaStream_t st = as_stream(stream);
   TNT_TRY(project_kv(D, ctx, w, st));
-  TNT_TRY(embed(D, ids, B, T, w.X0, nullptr, st));
-  // layer input lives in X0; run_layer uses X0/X1 internally, so ping-pong through cbuf-sized buffers:
-  // layer l reads `cur` and writes `nxt`; both are distinct from the internals (X0 is consumed first).
+  // sub-batches (engine.cuh): the layer chains of a few row ranges side by side, each on its own stream
+  SubBatches sb;
+  TNT_TRY(sub_plan(D, B, 1, 16, st, &sb));
   const int Ls = D->cfg.n_layers;
-  void* cur = w.X0;
-  for (int l = 0; l < Ls; ++l) {
-    const bool last = l == Ls - 1;
-    // Xin == w.X0 is safe: X0 is only overwritten by context_fc after its last use as residual.
-    void* out = last ? X_out : w.X0;
-    TNT_TRY(run_layer(D, l, ctx, w, cur, out, B, T, nullptr, nullptr, last ? attn_out : nullptr, last, st));
-    cur = out;
+  const size_t E = D->esz();
+  TNT_TRY(sub_fork(D, sb));
+  static const bool share_sms = [] { const char* e = getenv("TNT_SUB_SHARE_SMS"); return !(e && e[0] == '0'); }();
+  SmBudget budget(sb.n > 1 && share_sms ? num_sms() / sb.n : 0);
+  for (int i = 0; i < sb.n; ++i) {
+    const FwdWs wi = sb.n > 1 ? sub_ws(D, w, sb, i, B, T, ctx->S) : w;
+    const tnt_contexts ci = sb.n > 1 ? sub_ctx(*ctx, sb, i) : *ctx;
+    const int b0 = sb.b0[i], nb = ci.B;
+    TNT_TRY(embed(D, ids + static_cast<size_t>(b0) * T, nb, T, wi.X0, nullptr, sb.st[i]));
+    // layer l reads `cur` and writes `out`; Xin == X0 is safe: X0 is only overwritten by context_fc after its last use
+    // as residual.  The last layer writes batch-major rows straight into the caller's X (and attention weights).
+    void* cur = wi.X0;
+    for (int l = 0; l < Ls; ++l) {
+      const bool last = l == Ls - 1;
+      void* out = last ? static_cast<char*>(X_out) + static_cast<size_t>(b0) * T * D->cfg.d * E : wi.X0;
+      float* ao = nullptr;
+      if (last && attn_out && D->article_idx >= 0)
+        ao = attn_out + static_cast<size_t>(b0) * T * (ctx->S[D->article_idx] + 2);
+      TNT_TRY(run_layer(D, l, &ci, wi, cur, out, nb, T, nullptr, nullptr, ao, last, sb.st[i]));
+      cur = out;
+    }
   }
+  TNT_TRY(sub_join(D, sb));
   return TNT_OK;
 }
 

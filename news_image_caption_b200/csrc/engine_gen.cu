@@ -18,7 +18,7 @@ struct GenWs {
   FwdWs f;
   void* ring[TNT_MAX_LAYERS];
   int* pos; int* done_step; uint8_t* active; int64_t* cur; int64_t* tok; float* logp; void* ada;
-  size_t ada_bytes, total;
+  size_t ada_bytes, total;    // `ada` holds tnt_decoder::kMaxSub slots of ada_bytes (one per sub-batch)
 };
 
 GenWs carve_gen(const tnt_decoder* D, int B, const int* S, void* ws) {
@@ -38,8 +38,8 @@ GenWs carve_gen(const tnt_decoder* D, int B, const int* S, void* ws) {
   g.cur = static_cast<int64_t*>(take(sizeof(int64_t) * B));
   g.tok = static_cast<int64_t*>(take(sizeof(int64_t) * B));
   g.logp = static_cast<float*>(take(sizeof(float) * B));
-  g.ada_bytes = adasoftmax_workspace_bytes(D->ada, B, false);
-  g.ada = take(g.ada_bytes);
+  g.ada_bytes = al256(adasoftmax_workspace_bytes(D->ada, B, false));
+  g.ada = take(g.ada_bytes * tnt_decoder::kMaxSub);
   g.total = off;
   return g;
 }
@@ -87,16 +87,35 @@ __global__ void __launch_bounds__(1024) gen_update_kernel(const int64_t* tok, co
   }
 }
 
+// one decode step; the captions are cut into sub-batches (engine.cuh) whose chains run on their own streams: while one
+// sub-batch streams its K/V cache (HBM-bound), the others run their ~60 latency-bound small launches
 int gen_step(tnt_decoder* D, const tnt_contexts* ctx1, const GenWs& g, int B, int L, int eos, int64_t* ids_out,
-             float* logp_out, cudaStream_t st) {
-  tnt_embed_params e = {};
-  e.ids = g.cur; e.table = D->table; e.pos_table = D->pos_table; e.out = g.f.X0; e.ldo = D->cfg.d; e.start_pos = g.pos;
-  e.B = B; e.T = 1; e.d = D->cfg.d; e.n_pos = D->cfg.max_positions; e.pad_idx = D->cfg.pad_idx; e.dtype = D->cfg.dtype;
-  e.vocab = D->cfg.vocab; e.error_flags = D->err_flags;
-  TNT_TRY(tnt_embed_fwd(&e, st));
-  for (int l = 0; l < D->cfg.n_layers; ++l)
-    TNT_TRY(run_layer(D, l, ctx1, g.f, g.f.X0, g.f.X0, B, 1, g.ring[l], g.pos, nullptr, false, st));
-  TNT_TRY(adasoftmax_greedy(D->ada, g.f.X0, D->cfg.d, B, g.tok, g.logp, g.ada, g.ada_bytes, st));
+             float* logp_out, const SubBatches& sb0, cudaStream_t st) {
+  SubBatches sb = sb0;
+  sb.st[0] = st;                                   // the stream being issued on / captured
+  const size_t E = D->esz(), d = D->cfg.d;
+  TNT_TRY(sub_fork(D, sb));
+  static const bool share_sms = [] { const char* e = getenv("TNT_SUB_SHARE_SMS"); return !(e && e[0] == '0'); }();
+  SmBudget budget(sb.n > 1 && share_sms ? num_sms() / sb.n : 0);
+  for (int i = 0; i < sb.n; ++i) {
+    const FwdWs f = sb.n > 1 ? sub_ws(D, g.f, sb, i, B, 1, ctx1->S) : g.f;
+    const tnt_contexts ci = sb.n > 1 ? sub_ctx(*ctx1, sb, i) : *ctx1;
+    const int b0 = sb.b0[i], nb = ci.B;
+    cudaStream_t si = sb.st[i];
+    tnt_embed_params e = {};
+    e.ids = g.cur + b0; e.table = D->table; e.pos_table = D->pos_table; e.out = f.X0; e.ldo = D->cfg.d; e.start_pos = g.pos;
+    e.B = nb; e.T = 1; e.d = D->cfg.d; e.n_pos = D->cfg.max_positions; e.pad_idx = D->cfg.pad_idx; e.dtype = D->cfg.dtype;
+    e.vocab = D->cfg.vocab; e.error_flags = D->err_flags;
+    TNT_TRY(tnt_embed_fwd(&e, si));
+    for (int l = 0; l < D->cfg.n_layers; ++l) {
+      // ring [K-1][nb][d] of this sub-batch: a private block of the layer's ring memory
+      void* ring = static_cast<char*>(g.ring[l]) + static_cast<size_t>(std::max(D->cfg.kernels[l] - 1, 1)) * b0 * d * E;
+      TNT_TRY(run_layer(D, l, &ci, f, f.X0, f.X0, nb, 1, ring, g.pos, nullptr, false, si));
+    }
+    TNT_TRY(adasoftmax_greedy(D->ada, f.X0, D->cfg.d, nb, g.tok + b0, g.logp + b0, static_cast<char*>(g.ada) + i * g.ada_bytes,
+                              g.ada_bytes, si));
+  }
+  TNT_TRY(sub_join(D, sb));
   gen_update_kernel<<<1, 1024, 0, st>>>(g.tok, g.logp, B, L, eos, D->cfg.pad_idx, g.cur, g.active, ids_out, logp_out, g.pos);
   TNT_LAUNCHED();
   return TNT_OK;
@@ -278,8 +297,10 @@ extern "C" int tnt_decoder_generate(tnt_decoder* D, const int64_t* seed, const t
   c1.T = 1;
   gen_init_kernel<<<1, 1024, 0, st>>>(seed, B, gen_len, eos, g.cur, g.active, ids_out, g.pos);
   TNT_LAUNCHED();
-  TNT_TRY(project_kv(D, &c1, g.f, st, true));
-  TNT_TRY(run_steps(gen_len, st, [&](cudaStream_t s) { return gen_step(D, &c1, g, B, gen_len, eos, ids_out, logp_out, s); }));
+  SubBatches sb;
+  TNT_TRY(sub_plan(D, B, 1, 32, st, &sb));
+  TNT_TRY(project_kv(D, &c1, g.f, st, true, &sb));
+  TNT_TRY(run_steps(gen_len, st, [&](cudaStream_t s) { return gen_step(D, &c1, g, B, gen_len, eos, ids_out, logp_out, sb, s); }));
   if (steps_host) {
     int two[2];
     TNT_CUDA(cudaMemcpyAsync(two, g.pos, sizeof(two), cudaMemcpyDeviceToHost, st));

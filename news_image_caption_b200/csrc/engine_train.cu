@@ -51,10 +51,10 @@ struct TrainWs {
   void *dAO, *dCAT, *dCATp;                    // [N, ns*d]
   void *raw;                                   // [N, 2d]
   PGradBufs pg[2];                             // what the parameter-gradient stream reads, by layer parity
-  float* dW;                                   // fp32 scratch for weight-normed matrices / K-V / embedding grads
+  float* dW[tnt_decoder::kSideStreams];        // fp32 scratch for weight-normed matrices / K-V grads, one per side stream
   size_t dW_floats;
   float* attn_scr;                             // [B, H, T, D] fp32
-  float* vecs;                                 // [L*2d] fp32 scratch (K/V bias rows)
+  float* vecs[tnt_decoder::kSideStreams];      // [L*2d] fp32 scratch (K/V bias rows), one per side stream
   int *band_rows, *band_loc, *band_cnt, *band_head;
   void *G, *Hrows, *dH;                        // embedding backward [N, d]
   void* loss_fwd; size_t loss_fwd_bytes;
@@ -102,10 +102,10 @@ TrainWs carve_train(const tnt_decoder* D, int B, int T, const int* S, void* ws) 
   size_t dw = std::max<size_t>(2 * d * d, static_cast<size_t>(c.ffn) * d);
   dw = std::max(dw, d * ns * d);
   dw = std::max(dw, L * 2 * d * max_kdim);
-  w.dW = static_cast<float*>(take(dw * sizeof(float)));
+  for (float*& p : w.dW) p = static_cast<float*>(take(dw * sizeof(float)));
   w.dW_floats = dw;
   w.attn_scr = static_cast<float*>(take(N * d * sizeof(float)));
-  w.vecs = static_cast<float*>(take(L * 2 * d * sizeof(float)));
+  for (float*& p : w.vecs) p = static_cast<float*>(take(L * 2 * d * sizeof(float)));
   w.band_rows = static_cast<int*>(take(sizeof(int) * N * TNT_MAX_CLUSTERS));
   w.band_loc = static_cast<int*>(take(sizeof(int) * N * TNT_MAX_CLUSTERS));
   w.band_cnt = static_cast<int*>(take(sizeof(int) * TNT_MAX_CLUSTERS));
@@ -125,8 +125,9 @@ struct Ctx {
   cudaStream_t st;
   int dt;
   const tnt_dropout_config* dr;     // this step's dropout (seed already advanced) or NULL
-  cudaStream_t side = nullptr;      // parameter-gradient stream (NULL: everything on `st`)
-  bool side_pending = false;        // work issued on `side` since the last join
+  int n_side = 0;                   // parameter-gradient streams in use (0: everything on `st`)
+  int job = 0;                      // side stream (and scratch slot) of the parameter-gradient job being issued
+  bool side_pending = false;        // work issued on a side stream since the last join
   float* grad(const std::string& key) {
     auto it = D->grads.find(key);
     return it == D->grads.end() ? nullptr : it->second;
@@ -162,29 +163,34 @@ int ln_bwd(Ctx& c, const void* x, long ldx, const void* dy, long lddy, void* dx,
   return tnt_layernorm_bwd(&p, c.st);
 }
 
-// Parameter-gradient stream.  The backward's critical path is the DATA-gradient chain (dX flows from kernel to kernel,
+// Parameter-gradient streams.  The backward's critical path is the DATA-gradient chain (dX flows from kernel to kernel,
 // every launch latency-bound at B*T = 2048 rows); the weight-gradient GEMMs, the weight-norm backward and the bias column
-// sums only consume what that chain produces.  They are issued on `side`, so they fill the SMs the chain leaves idle:
-//   side_fork  -- everything issued on `st` so far is visible to the work that follows on `side` (call it right after the
-//                 producer of a tensor the side work reads, before the next chain kernel is issued);
+// sums only consume what that chain produces.  Each parameter is one JOB (weight-gradient GEMM -> weight-norm backward,
+// bias column sum) issued on a side stream, round-robin over a few of them -- the jobs are as latency-bound as the chain,
+// one stream alone fell 0.75 ms behind it:
+//   side_fork  -- starts a job: picks the next side stream, which then sees everything issued on `st` so far (call it right
+//                 after the producer of the tensor the job reads, before the next chain kernel is issued);
 //   side_join  -- `st` waits for all side work issued so far.
-// What the side work reads is never rewritten inside a layer (PGradBufs); the cross-layer reuse is ordered by
-// tnt_decoder::side_layer_done (layer_bwd).  w.dW / w.vecs are touched by side work only, so they are ordered in-stream.
+// What the jobs read is never rewritten inside a layer (PGradBufs); the cross-layer reuse is ordered by
+// tnt_decoder::side_layer_done (layer_bwd).  Scratch (w.dW / w.vecs) is per side stream, so it is ordered in-stream.
 int side_fork(Ctx& c) {
-  if (!c.side) return TNT_OK;
+  if (!c.n_side) return TNT_OK;
+  c.job = (c.job + 1) % c.n_side;
   TNT_CUDA(cudaEventRecord(c.D->side_fork, c.st));
-  TNT_CUDA(cudaStreamWaitEvent(c.side, c.D->side_fork, 0));
+  TNT_CUDA(cudaStreamWaitEvent(c.D->side_streams[c.job], c.D->side_fork, 0));
   c.side_pending = true;
   return TNT_OK;
 }
 int side_join(Ctx& c) {
-  if (!c.side || !c.side_pending) return TNT_OK;
-  TNT_CUDA(cudaEventRecord(c.D->side_join, c.side));
-  TNT_CUDA(cudaStreamWaitEvent(c.st, c.D->side_join, 0));
+  if (!c.n_side || !c.side_pending) return TNT_OK;
+  for (int k = 0; k < c.n_side; ++k) {
+    TNT_CUDA(cudaEventRecord(c.D->side_join[k], c.D->side_streams[k]));
+    TNT_CUDA(cudaStreamWaitEvent(c.st, c.D->side_join[k], 0));
+  }
   c.side_pending = false;
   return TNT_OK;
 }
-inline cudaStream_t pstream(Ctx& c) { return c.side ? c.side : c.st; }
+inline cudaStream_t pstream(Ctx& c) { return c.n_side ? c.D->side_streams[c.job] : c.st; }
 // weight-gradient GEMM (TN: reduction over the tokens) on the parameter-gradient stream
 template <typename... Args>
 int wgemm(Ctx& c, Args... args) { return gemm_on(pstream(c), c.dt, TNT_TN, EPI_NONE, args...); }
@@ -277,7 +283,9 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
   const tnt_dropout_config* dr = c.dr;
   const float p_out = dr ? dr->dropout : 0.f;
   // this layer rewrites the PGradBufs set layer l+2 used: its parameter-gradient work must have read them
-  if (c.side && l + 2 < cf.n_layers) TNT_CUDA(cudaStreamWaitEvent(c.st, D->side_layer_done[l + 2], 0));
+  if (l + 2 < cf.n_layers)
+    for (int k = 0; k < c.n_side; ++k)
+      TNT_CUDA(cudaStreamWaitEvent(c.st, D->side_layer_done[(l + 2) * tnt_decoder::kSideStreams + k], 0));
   // ---- final LayerNorm and feed-forward: Xout = LN(yf), yf = drop(fc2(drop_relu(relu(fc1(X0))))) + X0
   void* dyf = p_out > 0.f ? w.gB : G.gffn;        // gradient w.r.t. yf; G.gffn = the same with the fc2 dropout mask applied
   TNT_TRY(ln_bwd(c, a.yf, d, w.gA, d, dyf, d, L.ln_f_g, c.grad(p + "final_layer_norm.weight"),
@@ -285,21 +293,21 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
   if (p_out > 0.f)
     TNT_TRY(dropout_apply(dyf, d, nullptr, 0, G.gffn, d, N, d, dt, drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_FFN_OUT)), c.st));
   TNT_TRY(side_fork(c));
-  TNT_TRY(wgemm(c, G.gffn, d, a.F, ffn, w.dW, ffn, d, ffn, N, TNT_F32));
-  TNT_TRY(linear_param_grads(c, p + "fc2.", w.dW, d, ffn, false));
+  TNT_TRY(wgemm(c, G.gffn, d, a.F, ffn, w.dW[c.job], ffn, d, ffn, N, TNT_F32));
+  TNT_TRY(linear_param_grads(c, p + "fc2.", w.dW[c.job], d, ffn, false));
   TNT_TRY(bias_grad(c, p + "fc2.bias", G.gffn, d, N, d, false));
   // a.F holds the dropped-out ReLU output: F > 0 iff kept and active, and the kept elements carry 1 / (1 - p_relu)
   const float relu_scale = (dr && dr->relu_dropout > 0.f) ? 1.f / (1.f - dr->relu_dropout) : 0.f;
   TNT_TRY(gemm(c, TNT_NN, EPI_RELU_BWD, G.gffn, d, L.wf2, ffn, G.dF, ffn, N, ffn, d, dt, a.F, ffn, nullptr, relu_scale));
   TNT_TRY(side_fork(c));
-  TNT_TRY(wgemm(c, G.dF, ffn, a.X0, d, w.dW, d, ffn, d, N, TNT_F32));
-  TNT_TRY(linear_param_grads(c, p + "fc1.", w.dW, ffn, d, false));
+  TNT_TRY(wgemm(c, G.dF, ffn, a.X0, d, w.dW[c.job], d, ffn, d, N, TNT_F32));
+  TNT_TRY(linear_param_grads(c, p + "fc1.", w.dW[c.job], ffn, d, false));
   TNT_TRY(bias_grad(c, p + "fc1.bias", G.dF, ffn, N, ffn, false));
   TNT_TRY(gemm(c, TNT_NN, EPI_RESIDUAL, G.dF, ffn, L.wf1, d, G.dX0, d, N, d, ffn, dt, dyf, d));       // dX0
   // ---- context_fc over the concatenated, layer-normed per-source branches
   TNT_TRY(side_fork(c));
-  TNT_TRY(wgemm(c, G.dX0, d, a.CATln, nsd, w.dW, nsd, d, ns * d, N, TNT_F32));
-  TNT_TRY(linear_param_grads(c, p + "context_fc.", w.dW, d, ns * d, false));
+  TNT_TRY(wgemm(c, G.dX0, d, a.CATln, nsd, w.dW[c.job], nsd, d, ns * d, N, TNT_F32));
+  TNT_TRY(linear_param_grads(c, p + "context_fc.", w.dW[c.job], d, ns * d, false));
   TNT_TRY(bias_grad(c, p + "context_fc.bias", G.dX0, d, N, d, false));
   TNT_TRY(gemm(c, TNT_NN, EPI_NONE, G.dX0, d, L.wc, nsd, w.dCAT, nsd, N, ns * d, d, dt));
   void* dcatp = p_out > 0.f ? w.dCATp : G.gop;    // gradient w.r.t. CATpre; G.gop = the same with the out_proj dropout mask
@@ -313,11 +321,11 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
   if (p_out > 0.f)
     TNT_TRY(dropout_apply(dcatp, nsd, nullptr, 0, G.gop, nsd, N, ns * d, dt,
                           drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_ATTN_OUT), nsd), c.st));
-  TNT_TRY(side_fork(c));
   for (int s = 0; s < ns; ++s) {
     const std::string at = p + "context_attns." + cf.source_names[s] + ".";
     float* dwo = c.grad(at + "out_proj.weight");
     TNT_CHECK_ARG(dwo, "train: gradient buffer for '%sout_proj.weight' missing", at.c_str());
+    TNT_TRY(side_fork(c));
     TNT_TRY(wgemm(c, off(G.gop, static_cast<size_t>(s) * d, E), nsd, off(a.AO, static_cast<size_t>(s) * d, E), nsd, dwo, d, d, d, N,
                   TNT_F32));
     TNT_TRY(bias_grad(c, at + "out_proj.bias", off(G.gop, static_cast<size_t>(s) * d, E), nsd, N, d, false));
@@ -355,8 +363,8 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
   if (p_out > 0.f)
     TNT_TRY(dropout_apply(dyc, d, nullptr, 0, G.gl2, d, N, d, dt, drop_site(dr, p_out, TNT_DROP_SITE(l, TNT_DROP_CONV_OUT)), c.st));
   TNT_TRY(side_fork(c));
-  TNT_TRY(wgemm(c, G.gl2, d, a.cbuf, d, w.dW, d, d, d, N, TNT_F32));
-  TNT_TRY(linear_param_grads(c, p + "linear2.", w.dW, d, d, false));
+  TNT_TRY(wgemm(c, G.gl2, d, a.cbuf, d, w.dW[c.job], d, d, d, N, TNT_F32));
+  TNT_TRY(linear_param_grads(c, p + "linear2.", w.dW[c.job], d, d, false));
   TNT_TRY(bias_grad(c, p + "linear2.bias", G.gl2, d, N, d, false));
   TNT_TRY(gemm(c, TNT_NN, EPI_NONE, G.gl2, d, L.w2, d, w.gC, d, N, d, d, dt));                        // gC = dcbuf
   {
@@ -378,8 +386,8 @@ int layer_bwd(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, const void* Xi
   TNT_TRY(gemm(c, TNT_NT, EPI_NONE, X1in, d, L.w1, d, w.raw, 2 * d, N, 2 * d, d, dt, nullptr, 0, nullptr, 0.f, L.b1));
   TNT_TRY(glu_bwd(w.raw, 2 * d, w.gC, d, G.draw, 2 * d, N, d, dt, c.st));
   TNT_TRY(side_fork(c));
-  TNT_TRY(wgemm(c, G.draw, 2 * d, X1in, d, w.dW, d, 2 * d, d, N, TNT_F32));
-  TNT_TRY(linear_param_grads(c, p + "linear1.", w.dW, 2 * d, d, true));
+  TNT_TRY(wgemm(c, G.draw, 2 * d, X1in, d, w.dW[c.job], d, 2 * d, d, N, TNT_F32));
+  TNT_TRY(linear_param_grads(c, p + "linear1.", w.dW[c.job], 2 * d, d, true));
   TNT_TRY(bias_grad(c, p + "linear1.bias", G.draw, 2 * d, N, 2 * d, true));
   if (in_drop) {                                  // gA = dXin = drop(draw . W1) + dyc
     TNT_TRY(gemm(c, TNT_NN, EPI_NONE, G.draw, 2 * d, L.w1, d, w.gC, d, N, d, 2 * d, dt));
@@ -406,12 +414,12 @@ int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, int s) {
   TNT_CHECK_ARG(gk && gv && gb, "train: gradient buffer for '%sbias_k / bias_v / in_proj_bias' missing", at.c_str());
   TNT_TRY(side_fork(c));
   cudaStream_t ss = pstream(c);
-  TNT_TRY(kv_extra_grad(dkv, ldkv, S, B, 2 * d, w.vecs, c.dt, ss));        // the learned extra key row (index S)
-  TNT_CUDA(cudaMemcpyAsync(gk, w.vecs, sizeof(float) * d, cudaMemcpyDeviceToDevice, ss));
-  TNT_CUDA(cudaMemcpyAsync(gv, w.vecs + d, sizeof(float) * d, cudaMemcpyDeviceToDevice, ss));
+  TNT_TRY(kv_extra_grad(dkv, ldkv, S, B, 2 * d, w.vecs[c.job], c.dt, ss));        // the learned extra key row (index S)
+  TNT_CUDA(cudaMemcpyAsync(gk, w.vecs[c.job], sizeof(float) * d, cudaMemcpyDeviceToDevice, ss));
+  TNT_CUDA(cudaMemcpyAsync(gv, w.vecs[c.job] + d, sizeof(float) * d, cudaMemcpyDeviceToDevice, ss));
   TNT_TRY(colsum(dkv, ldkv, S * B, 2 * d, nullptr, gb + d, c.dt, false, false, ss));
   float* gi = c.grad(at + "in_proj_weight");
-  float* dst = gi ? gi + static_cast<size_t>(d) * d : w.dW;
+  float* dst = gi ? gi + static_cast<size_t>(d) * d : w.dW[c.job];
   // A long reduction (the article: S*B = 32768 rows) over only (2d/128) x (kd/256) output tiles leaves most SMs idle, and
   // narrower tiles are L2->SM bound (128 x 128 tiles: 213 us = 46 % of the tensor peak).  The rows are split into G
   // groups of one grouped launch -- wide tiles on every SM -- whose fp32 partials are summed afterwards.
@@ -424,7 +432,7 @@ int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, int s) {
     if (need > w.dW_floats || (static_cast<size_t>(2) * d * kd) % 4) G = 1;
   }
   if (G > 1) {
-    float* parts = w.dW + (gi ? 0 : static_cast<size_t>(2) * d * kd);
+    float* parts = w.dW[c.job] + (gi ? 0 : static_cast<size_t>(2) * d * kd);
     TNT_TRY(wgemm(c, dkv, ldkv, ctx->memory[s], kd, parts, kd, 2 * d, kd, Kr / G, TNT_F32, nullptr, 0, nullptr, 0.f,
                   nullptr, G, static_cast<long>(Kr / G) * ldkv, static_cast<long>(Kr / G) * kd, 0, static_cast<long>(2) * d * kd));
     TNT_TRY(sum_partials(dst, parts, G, static_cast<long>(2) * d * kd, ss));
@@ -436,8 +444,8 @@ int kv_param_grads(Ctx& c, const tnt_contexts* ctx, TrainWs& w, int l, int s) {
   if (!gi) {
     float *gwk = c.grad(at + "k_proj_weight"), *gwv = c.grad(at + "v_proj_weight");
     TNT_CHECK_ARG(gwk && gwv, "train: gradient buffer for '%sk/v_proj_weight' missing", at.c_str());
-    TNT_CUDA(cudaMemcpyAsync(gwk, w.dW, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, ss));
-    TNT_CUDA(cudaMemcpyAsync(gwv, w.dW + static_cast<size_t>(d) * kd, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, ss));
+    TNT_CUDA(cudaMemcpyAsync(gwk, w.dW[c.job], sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, ss));
+    TNT_CUDA(cudaMemcpyAsync(gwv, w.dW[c.job] + static_cast<size_t>(d) * kd, sizeof(float) * d * kd, cudaMemcpyDeviceToDevice, ss));
   }
   return TNT_OK;
 }
@@ -543,23 +551,33 @@ int step_setup(tnt_decoder* D, const tnt_contexts* ctx, void* workspace, size_t 
     set_error("%s: workspace %zu < %zu", who, workspace_bytes, s->w.total);
     return TNT_ERR_WORKSPACE;
   }
-  static const bool use_side = !(getenv("TNT_TRAIN_SIDE_STREAM") && atoi(getenv("TNT_TRAIN_SIDE_STREAM")) == 0);
-  if (use_side && !D->side_stream) {
+  // TNT_TRAIN_SIDE_STREAMS = 0..4 parameter-gradient streams (default 3; TNT_TRAIN_SIDE_STREAM=0 also switches them off)
+  static const int want_side = [] {
+    const char* off1 = getenv("TNT_TRAIN_SIDE_STREAM");
+    if (off1 && atoi(off1) == 0) return 0;
+    const char* n = getenv("TNT_TRAIN_SIDE_STREAMS");
+    return n ? std::max(0, std::min(atoi(n), static_cast<int>(tnt_decoder::kSideStreams))) : 3;
+  }();
+  if (want_side && !D->side_fork) {
     int lo = 0, hi = 0;
     TNT_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-    // measured (B = 64, one GPU): highest priority 7.05 ms per step, lowest 7.12 ms -- the parameter-gradient kernels are
-    // short, and letting them in first keeps them from lingering beside three or four chain kernels (TNT_SIDE_PRIO=lo: A/B)
+    // measured (B = 64, one GPU, one side stream): highest priority 7.05 ms per step, lowest 7.12 ms -- the parameter-gradient
+    // kernels are short, and letting them in first keeps them from lingering beside three or four chain kernels
     const char* pe = getenv("TNT_SIDE_PRIO");
-    TNT_CUDA(cudaStreamCreateWithPriority(&D->side_stream, cudaStreamNonBlocking, (pe && pe[0] == 'l') ? lo : hi));
+    for (int k = 0; k < want_side; ++k) {
+      TNT_CUDA(cudaStreamCreateWithPriority(&D->side_streams[k], cudaStreamNonBlocking, (pe && pe[0] == 'l') ? lo : hi));
+      TNT_CUDA(cudaEventCreateWithFlags(&D->side_join[k], cudaEventDisableTiming));
+    }
+    TNT_CUDA(cudaStreamCreateWithFlags(&D->stage_stream, cudaStreamNonBlocking));
     TNT_CUDA(cudaEventCreateWithFlags(&D->side_fork, cudaEventDisableTiming));
-    TNT_CUDA(cudaEventCreateWithFlags(&D->side_join, cudaEventDisableTiming));
+    D->n_side = want_side;
   }
   while (static_cast<int>(D->stage_events.size()) < Ls + 2) {
     cudaEvent_t e;
     TNT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     D->stage_events.push_back(e);
   }
-  while (static_cast<int>(D->side_layer_done.size()) < Ls) {
+  while (static_cast<int>(D->side_layer_done.size()) < Ls * tnt_decoder::kSideStreams) {
     cudaEvent_t e;
     TNT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     D->side_layer_done.push_back(e);
@@ -601,7 +619,7 @@ int train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, co
   const tnt_decoder_config& cf = D->cfg;
   const int B = ctx->B, T = ctx->T, N = B * T, d = cf.d, ns = cf.n_sources, Ls = cf.n_layers;
   Ctx c{D, st, cf.dtype, dr};
-  c.side = D->side_stream;
+  c.n_side = D->n_side;
   if (!ext) TNT_TRY(adasoftmax_nll(D->ada, w.Xbt, d, target, N, cf.pad_idx, out2, w.loss_fwd, w.loss_fwd_bytes, st));
   // ---------------- backward: loss
   const int nt = cf.n_clusters - 1;
@@ -625,12 +643,18 @@ int train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, co
   for (int l = Ls - 1; l >= 0; --l) {
     const void* xin = l == 0 ? w.emb : w.act[l - 1].Xout;
     TNT_TRY(layer_bwd(c, ctx, w, l, xin, (ext && l == Ls - 1) ? ext->dattn : nullptr));
-    // stage Ls - l is final when the chain AND the parameter-gradient work of layer l are: the event is recorded on the
-    // parameter-gradient stream after it has caught up with the chain (the chain itself does not wait)
-    if (c.side) {
-      TNT_TRY(side_fork(c));
-      TNT_CUDA(cudaEventRecord(D->side_layer_done[l], c.side));
-      TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], c.side));
+    // stage Ls - l is final when the chain AND the parameter-gradient work of layer l are: the event is recorded on a
+    // kernel-less stream that waits for both (neither the chain nor the side streams wait for each other here)
+    if (c.n_side) {
+      cudaStream_t s0 = D->stage_stream;
+      for (int k = 0; k < c.n_side; ++k) {
+        cudaEvent_t done = D->side_layer_done[l * tnt_decoder::kSideStreams + k];
+        TNT_CUDA(cudaEventRecord(done, D->side_streams[k]));
+        TNT_CUDA(cudaStreamWaitEvent(s0, done, 0));
+      }
+      TNT_CUDA(cudaEventRecord(D->side_fork, st));
+      TNT_CUDA(cudaStreamWaitEvent(s0, D->side_fork, 0));
+      TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], s0));
     } else {
       TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], st));
     }
@@ -712,7 +736,7 @@ extern "C" int tnt_decoder_target_logprob(tnt_decoder* D, const int64_t* target,
   TNT_CHECK_ARG(D->pending_ws == workspace, "decoder_target_logprob: no matching tnt_decoder_train_forward_ext on this workspace");
   StepSetup s;
   TNT_TRY(step_setup(D, ctx, workspace, workspace_bytes, "decoder_target_logprob", &s));
-  float* scratch2 = s.w.vecs;                    // the AdaptiveLoss sum of the statistics pass is not used here
+  float* scratch2 = s.w.vecs[0];                   // the AdaptiveLoss sum of the statistics pass is not used here
   return adasoftmax_target_logprob(D->ada, s.w.Xbt, D->cfg.d, target, ctx->B * ctx->T, D->cfg.pad_idx, lp_out, scratch2,
                                    s.w.loss_fwd, s.w.loss_fwd_bytes, as_stream(stream));
 }

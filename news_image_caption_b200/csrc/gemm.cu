@@ -16,7 +16,11 @@ namespace tnt {
 // ============================================================================ tcgen05 kernel
 namespace tc {
 constexpr int BM = 128, BK = 64, UMMA_K = 16;
-constexpr int kThreads = 192;             // warp 0: TMA producer, warp 1: MMA issuer, warps 2-5: epilogue
+// warp 0: TMA producer, warp 1: MMA issuer, warps 2..: epilogue (4 warps = one per TMEM lane quadrant).  The log-sum-exp
+// epilogue (EPI_LSE: no output matrix, ~11 instructions and one MUFU per logit) is the whole cost of the adaptive-softmax
+// GEMMs -- K = 64 .. 1024 against up to 30265 columns -- and with one warp per scheduler it ran at the latency of its
+// dependent chains; it gets 8 warps, two per quadrant, each owning half of the tile's columns.
+template <int EPI> struct EpiWarps { static constexpr int n = EPI == EPI_LSE ? 8 : 4; static constexpr int threads = 64 + 32 * n; };
 constexpr int A_STAGE_BYTES = BM * BK * 2;
 constexpr uint32_t kTmemCols = 512;       // 2 accumulator stages x 256 fp32 columns
 constexpr int kAccStride = 256;
@@ -46,7 +50,7 @@ __device__ __forceinline__ void decode_tile(int tile, int m_tiles, int n_tiles, 
 // each CTA stages its own 128 A rows and BN/2 of the W rows, the leader issues tcgen05.mma.cta_group::2
 // (M = 256), so every CTA reads half as much B from shared memory / L2 per FLOP as in the CG = 1 form.
 template <int EPI, typename TOut, int CG>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(EpiWarps<EPI>::threads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, GemmArgs g,
                int BN, int stages, int n_tiles) {
   extern __shared__ uint8_t smem_raw[];
@@ -91,11 +95,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tfull[s], 1);
-      ptx::mbar_init(&tempty[s], 4 * CG);              // the leader waits for the epilogue warps of BOTH CTAs
+      ptx::mbar_init(&tempty[s], EpiWarps<EPI>::n * CG);   // the leader waits for the epilogue warps of BOTH CTAs
     }
     for (int s = 0; s < kSched; ++s) {
       ptx::mbar_init(&sfull[s], 1);
-      ptx::mbar_init(&sempty[s], 5);                   // the MMA warp + 4 epilogue warps have read the slot
+      ptx::mbar_init(&sempty[s], 1 + EpiWarps<EPI>::n);    // the MMA warp + the epilogue warps have read the slot
     }
     ptx::fence_barrier_init();
   }
@@ -279,6 +283,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else {
     // ------------------------------------------------------------ epilogue warps (TMEM -> regs -> HBM)
     const int q = warp & 3;                            // TMEM lane quadrant this warp may read
+    const int half = (warp - 2) >> 2;                  // EPI_LSE: which half of the tile's columns (0 for the 4-warp epilogues)
+    const int halves = EPI == EPI_LSE ? g.lse_halves : 1;
     const int nacc_e = CG == 1 ? g.nacc : 1;
     int cs = 0;
     uint32_t cph = 0;
@@ -304,8 +310,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       float* sb = sbias + as * 256;
       if (g.bias) {
         const float* bg = g.bias + grp * g.sbias + nt * BN;
-        for (int i = threadIdx.x - 64; i < BN; i += 128) sb[i] = (nt * BN + i < g.N) ? __ldg(bg + i) : 0.f;
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        for (int i = threadIdx.x - 64; i < BN; i += 32 * EpiWarps<EPI>::n) sb[i] = (nt * BN + i < g.N) ? __ldg(bg + i) : 0.f;
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * EpiWarps<EPI>::n) : "memory");
       }
       ptx::mbar_wait(&tfull[as], aph);
       ptx::tc_fence_after();
@@ -366,8 +372,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // (measured: software-pipelining these TMEM loads -- chunk c+1 in flight while chunk c is converted and stored -- is
       // SLOWER: forward 1.629 vs 1.600 ms, generation 25.55 vs 24.93 ms, training 8.29 vs 8.21 ms on one box; the epilogue is
       // not on the critical path, the extra 70 registers and the longer code are)
+      // EPI_LSE with two warps per quadrant: warp-half h owns chunks [h * BN/64, (h + 1) * BN/64) and its own partial record
+      const int c_lo = halves == 2 ? half * (BN / 64) : (half ? nch : 0);
+      const int c_hi = halves == 2 ? min(nch, c_lo + BN / 64) : nch;
       {
-        for (int c = 0; c < nch; ++c) {
+        for (int c = c_lo; c < c_hi; ++c) {
           uint32_t v[32];
           ptx::tmem_ld_32x32(taddr + c * 32, v);
           ptx::tmem_ld_wait();
@@ -381,8 +390,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           process(v, c);
         }
       }
-      if (EPI == EPI_LSE && row < M)
-        g.partials[static_cast<long>(row) * g.n_tiles + nt] = make_float4(la.m, la.s, __int_as_float(la.arg), la.tz);
+      if (EPI == EPI_LSE && row < M && half < halves)
+        g.partials[static_cast<long>(row) * g.n_tiles + nt * halves + half] = make_float4(la.m, la.s, __int_as_float(la.arg), la.tz);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) {
@@ -647,7 +656,7 @@ static int launch_tc_cg(const GemmArgs& g, int BN, cudaStream_t st) {
   }
   // more than one tile per CTA somewhere, or fewer tiles than SMs: either way the counter decides who works
   ga.tile_ctr = (CG == 1 && g_dynamic_tiles) ? next_tile_ctr() : nullptr;
-  TNT_CUDA(launch_pdl(kern, dim3(grid), dim3(tc::kThreads), smem, st, CG, tmA, tmW, ga, BN, stages, n_tiles));
+  TNT_CUDA(launch_pdl(kern, dim3(grid), dim3(tc::EpiWarps<EPI>::threads), smem, st, CG, tmA, tmW, ga, BN, stages, n_tiles));
   TNT_LAUNCHED();
   variant_hit(CG == 2 ? V_GEMM_TC_PAIR : V_GEMM_TC_1CTA);
   return TNT_OK;
@@ -700,6 +709,7 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
   if (p->M == 0) return TNT_OK;
   GemmArgs g;
   g.tile_ctr = nullptr;
+  g.lse_halves = 1;
   g.a = p->a; g.w = p->w; g.bias = p->bias; g.res = p->residual; g.c = p->c;
   g.lda = p->lda; g.ldw = p->ldw; g.ldr = p->ldr; g.ldc = p->ldc;
   g.M = p->M; g.N = p->N; g.K = p->K;
@@ -755,6 +765,10 @@ int launch_gemm(const tnt_linear_params* p, int epi_override, const LseExtra* ls
     }
   }
   g.n_tiles = (g.N + BN - 1) / BN;
+  // tcgen05 log-sum-exp epilogue: two partial records per tile (one per warp-half) once the tile has >= 4 column chunks;
+  // 2 * ceil(N / BN) <= ceil(N / 32) records per row, the size lse_partials_bytes() reserves
+  g.lse_halves = (epi == EPI_LSE && use_tc && BN >= 128) ? 2 : 1;
+  g.n_tiles *= g.lse_halves;
   if (n_tiles_out) *n_tiles_out = g.n_tiles;
   switch (epi) {
     case EPI_NONE: return dispatch_dtype<EPI_NONE>(g, p->dtype_in, p->dtype_out, BN, CG, g_force_simt, st);

@@ -19,6 +19,7 @@ struct GemmArgs {
   const int* target;        // [M] cluster-local target column or < 0
   float4* partials;         // [M, n_tiles] (max, sumexp, argmax bits, target logit or 0)
   int n_tiles;
+  int lse_halves;           // tcgen05 kernel: partial records per column tile (2: one per half of the tile's columns)
   int n_lse;                // columns [0, n_lse) take part in max / sum / argmax ...
   float* side; long side_ld;  // ... columns [n_lse, N) are written raw to side[row, col - n_lse]
   // operand layouts: a_mn = A stored [K, M] (TN), b_mn = W stored [K, N] (NN / TN)
@@ -102,8 +103,9 @@ __device__ __forceinline__ void epilogue_store(const GemmArgs& g, int grp, int m
   }
   if (EPI == EPI_RELU_BWD) {
     const TOut* rrow = reinterpret_cast<const TOut*>(g.res) + grp * g.sres + static_cast<long>(m) * g.ldr;
-    if (NC % 8 == 0 && g.vec_ok && n0 + NC <= g.N) {       // 16-byte loads of the saved activation (scalar loads: 32 sectors
-#pragma unroll                                             // per instruction and warp -- the epilogue was 3x the k-loop)
+    // 16-byte loads of the saved activation (scalar loads touch 32 sectors per instruction: the epilogue was 3x the k-loop)
+    if (NC % 8 == 0 && g.vec_ok && n0 + NC <= g.N) {
+#pragma unroll
       for (int i = 0; i < NC; i += 8) {
         float t[8];
         load8(rrow + n0 + i, t);
@@ -205,6 +207,29 @@ __device__ __forceinline__ void zero_store(const GemmArgs& g, int grp, int m, in
 }
 
 // running (max, sumexp, argmax, target-logit) over a run of columns of one row
+// packed f32x2 arithmetic (sm_100: FFMA2 / FADD2) and the bare MUFU.EX2
+__device__ __forceinline__ uint64_t pack_f32x2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t add_f32x2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ float ptx_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 struct LseAcc {
   float m, s, tz;
   int arg;
@@ -219,28 +244,37 @@ struct LseAcc {
     }
     if (col == tgt) tz = z;
   }
-  // NC consecutive columns starting at col0, all valid: branch-free max/argmax pass, then ONE rescale
-  // of the running sum and NC exp2 (no data-dependent divergence inside the warp).
+  // NC consecutive columns starting at col0, all valid.  2.5 instructions per logit: the chunk maximum is a chain of 3-input
+  // FMNMX, the exponent arguments and the running sum are packed f32x2 (FFMA2 / FADD2, sm_100), one MUFU.EX2 per logit.
+  // The arg-max index is only looked for when the chunk raised the row maximum (a handful of chunks per row).  The first
+  // form of this function (select-based max / argmax, scalar FFMA + exp2f + FADD: 13 instructions per logit) made the
+  // adaptive-softmax GEMMs issue-bound: 25 M warp instructions, 51 us for 2048 x 30265 x 64 (ncu, profiles/).
   template <int NC>
   __device__ __forceinline__ void add_chunk(const float (&z)[NC], int col0, int tgt) {
+    static_assert(NC % 2 == 0, "NC");
     float cm = z[0];
-    int ca = 0;
 #pragma unroll
-    for (int i = 1; i < NC; ++i) {
-      const bool gt = z[i] > cm;
-      cm = gt ? z[i] : cm;
-      ca = gt ? i : ca;
-    }
+    for (int i = 1; i < NC; ++i) cm = fmaxf(cm, z[i]);
     if (cm > m) {
-      s *= exp2f((m - cm) * 1.4426950408889634f);
+      s *= ptx_ex2((m - cm) * 1.4426950408889634f);     // m = -inf -> 0
       m = cm;
+      int ca = 0;
+#pragma unroll
+      for (int i = NC - 1; i >= 0; --i) ca = z[i] == cm ? i : ca;   // lowest column wins a tie
       arg = col0 + ca;
     }
-    const float mb = m * 1.4426950408889634f;
-    float acc = 0.f;
+    const float mb = m * -1.4426950408889634f;
+    const uint64_t l2 = pack_f32x2(1.4426950408889634f, 1.4426950408889634f), nb = pack_f32x2(mb, mb);
+    uint64_t acc = pack_f32x2(0.f, 0.f);
 #pragma unroll
-    for (int i = 0; i < NC; ++i) acc += exp2f(fmaf(z[i], 1.4426950408889634f, -mb));
-    s += acc;
+    for (int i = 0; i < NC; i += 2) {
+      float a, b;
+      unpack_f32x2(fma_f32x2(pack_f32x2(z[i], z[i + 1]), l2, nb), a, b);
+      acc = add_f32x2(acc, pack_f32x2(ptx_ex2(a), ptx_ex2(b)));
+    }
+    float a, b;
+    unpack_f32x2(acc, a, b);
+    s += a + b;
     const int ti = tgt - col0;
     if (ti >= 0 && ti < NC) {
 #pragma unroll

@@ -58,18 +58,20 @@ def main():
     prof.export_chrome_trace(f)
     ev = [e for e in json.load(open(f))['traceEvents'] if e.get('cat') in ('kernel', 'gpu_memcpy', 'gpu_memset')]
     ev.sort(key=lambda e: e['ts'])
-    # a step starts at its embed_kernel launch (first kernel of every workload's step); take the middle one
-    marks = [i for i, e in enumerate(ev) if 'embed_kernel' in e['name']]
+    # a step starts at the first kv_extra_rows launch of its K/V projection (one per source, back to back); a decode step
+    # of the generation ends with its gen_update_kernel
     if a.workload == 'gen':
-        # one embed per decode step: take decode steps 10..11 of the second generate() call
+        marks = [i + 1 for i, e in enumerate(ev) if 'gen_update_kernel' in e['name']]
         per = len(marks) // 3
         i0, i1 = marks[per + 10], marks[per + 11]
     else:
+        marks = [i for i, e in enumerate(ev) if 'kv_extra_rows' in e['name'] and
+                 not any('kv_extra_rows' in m['name'] for m in ev[max(0, i - 4):i])]
         i0, i1 = marks[1], marks[2]
     step_ev = ev[i0:i1]
     t0 = step_ev[0]['ts']
     wall = ev[i1]['ts'] - t0
-    out = ['%s: one step = %d device ops, %.1f us wall (start of embed -> start of the next embed)' % (a.workload, len(step_ev), wall)]
+    out = ['%s: one step = %d device ops, %.1f us wall (first op of the step -> first op of the next)' % (a.workload, len(step_ev), wall)]
     # under PDL a kernel's recorded duration includes its wait for the predecessor: `excl_us` = the time by which this op
     # moved the stream's completion front (end - max(previous end, start)) is what the op really costs the step
     out.append('%9s %8s %8s %7s %4s  %s' % ('start_us', 'dur_us', 'excl_us', 'gap_us', 'strm', 'op'))
