@@ -399,13 +399,17 @@ int adasoftmax_logprob(const AdaSoftmax& a, const void* x, long ldx, int N, floa
 // by re-running the logits GEMM with the EPI_SMGRAD epilogue (bf16 dZ, never fp32 logits), then
 // dX = dZ . W (NN) and dW = dZ^T . X (TN).  Tail rows are gathered / scattered through the forward's row lists.
 struct AdaBwdWs {
-  float* row_lse; int* row_tgt; void* dz; void* dact; void* dxc; float* dhead; float* row_w;
-  long ldz;
+  // cluster c = 0: head, c = 1 + i: tail i.  Every cluster has buffers of its own: the clusters' chains (and their
+  // weight-gradient GEMMs) run side by side on different streams when the caller lends some (AdaSide)
+  float* row_lse[TNT_MAX_CLUSTERS]; int* row_tgt[TNT_MAX_CLUSTERS]; void* dz[TNT_MAX_CLUSTERS]; long ldz[TNT_MAX_CLUSTERS];
+  void* xc[TNT_MAX_CLUSTERS]; void* proj[TNT_MAX_CLUSTERS]; void* dact[TNT_MAX_CLUSTERS]; void* dxc[TNT_MAX_CLUSTERS];
+  float* row_w[TNT_MAX_CLUSTERS];
+  float* dhead;
   size_t total;
 };
 
 static AdaBwdWs carve_bwd(const AdaSoftmax& a, int N, void* ws) {
-  AdaBwdWs w;
+  AdaBwdWs w = {};
   const int nt = a.cuts.n - 1;
   size_t off = 0;
   auto take = [&](size_t bytes) {
@@ -413,17 +417,22 @@ static AdaBwdWs carve_bwd(const AdaSoftmax& a, int N, void* ws) {
     off += al256(bytes);
     return p;
   };
-  int max_cols = a.cuts.cut[0] + nt;
-  for (int i = 0; i < nt; ++i) max_cols = std::max(max_cols, a.cuts.cut[i + 1] - a.cuts.cut[i]);
-  w.ldz = (max_cols + 7) & ~7;
   const size_t E = dtype_size(a.dtype);
-  w.row_lse = static_cast<float*>(take(sizeof(float) * N));
-  w.row_tgt = static_cast<int*>(take(sizeof(int) * N));
-  w.dz = take(E * N * w.ldz);
-  w.dact = take(E * N * a.d);
-  w.dxc = take(E * N * a.d);
+  for (int c = 0; c <= nt; ++c) {
+    const int cols = c == 0 ? a.cuts.cut[0] + nt : a.cuts.cut[c] - a.cuts.cut[c - 1];
+    w.ldz[c] = (cols + 7) & ~7;
+    w.row_lse[c] = static_cast<float*>(take(sizeof(float) * N));
+    w.row_tgt[c] = static_cast<int*>(take(sizeof(int) * N));
+    w.dz[c] = take(E * N * w.ldz[c]);
+    if (c > 0) {
+      w.xc[c] = take(E * N * a.d);
+      w.proj[c] = take(E * N * a.d);
+      w.dact[c] = take(E * N * a.d);
+      w.dxc[c] = take(E * N * a.d);
+      w.row_w[c] = static_cast<float*>(take(sizeof(float) * N));
+    }
+  }
   w.dhead = static_cast<float*>(take(sizeof(float) * (a.cuts.cut[0] + nt) * a.d));
-  w.row_w = static_cast<float*>(take(sizeof(float) * N));
   w.total = off;
   return w;
 }
@@ -458,7 +467,7 @@ int gather_floats(const float* src, const int* rows, const int* count, int N, fl
 
 int adasoftmax_nll_bwd(const AdaSoftmax& a, const void* x, long ldx, int N, int pad, float gscale, void* ws_fwd,
                        void* dX, long lddx, float* d_head_words, float* d_class_proj, float* const* d_proj,
-                       float* const* d_out, void* ws, size_t ws_bytes, cudaStream_t st, const float* row_w) {
+                       float* const* d_out, void* ws, size_t ws_bytes, cudaStream_t st, const float* row_w, const AdaSide* sd) {
   // row_w != NULL: gradient of sum_r row_w[r] * (-lp[r]) with lp = adasoftmax_target_logprob (full log-softmax of the
   // target: the tail term counts for every tail row) instead of the AdaptiveLoss sum with its in-cluster ignore_index
   AdaWs f = carve(a, N, ws_fwd, false);
@@ -469,39 +478,62 @@ int adasoftmax_nll_bwd(const AdaSoftmax& a, const void* x, long ldx, int N, int 
   }
   const int nt = a.cuts.n - 1, d = a.d, dt = a.dtype, nh = a.cuts.cut[0] + nt;
   const size_t E = dtype_size(dt);
-  // stale rows of the gather / projection buffers must be finite (0 x NaN inside a 64-row reduction block)
-  TNT_CUDA(cudaMemsetAsync(f.xc, 0, E * N * d, st));
-  TNT_CUDA(cudaMemsetAsync(f.proj, 0, E * N * d, st));
-  // ---- head cluster
-  TNT_TRY(smgrad_rows_head(f.head_stats, f.side, f.head_t, N, nt, a.cuts.cut[0], pad, w.row_lse, w.row_tgt, st));
-  LseExtra ex = {w.row_tgt, nullptr, 0, nullptr, 0, w.row_lse, gscale};
-  ex.row_w = row_w;
-  TNT_TRY(gemm_call(x, ldx, a.head_w, d, w.dz, w.ldz, N, nh, d, dt, dt, TNT_NT, EPI_SMGRAD, nullptr, nullptr, 0, &ex, st));
-  TNT_TRY(gemm_call(w.dz, w.ldz, a.head_w, d, dX, lddx, N, d, nh, dt, dt, TNT_NN, EPI_NONE, nullptr, nullptr, 0, nullptr, st));
-  TNT_TRY(gemm_call(w.dz, w.ldz, x, ldx, w.dhead, d, nh, d, N, dt, TNT_F32, TNT_TN, EPI_NONE, nullptr, nullptr, 0, nullptr, st));
-  TNT_CUDA(cudaMemcpyAsync(d_head_words, w.dhead, sizeof(float) * a.cuts.cut[0] * d, cudaMemcpyDeviceToDevice, st));
-  if (nt > 0)
-    TNT_CUDA(cudaMemcpyAsync(d_class_proj, w.dhead + static_cast<size_t>(a.cuts.cut[0]) * d, sizeof(float) * nt * d,
-                             cudaMemcpyDeviceToDevice, st));
+  // The clusters are independent until their gradients meet in dX, and each is a chain of a few GEMMs with awkward shapes
+  // (a tail's data gradient reduces over up to 30265 columns into a handful of output tiles).  With streams lent by the
+  // caller (sd) every tail's chain runs on a stream of its own beside the head's (on st), the weight gradients -- nothing
+  // waits for them here -- follow on those streams, and st only waits for the tails' dxc before it scatter-adds them.
+  const bool par = sd && sd->n > 0;
+  auto tail_st = [&](int i) { return par ? sd->st[i % sd->n] : st; };
+  cudaStream_t head_wst = par ? sd->st[nt % sd->n] : st;
+  if (par) {
+    TNT_CUDA(cudaEventRecord(sd->fork, st));
+    for (int k = 0; k < sd->n; ++k) TNT_CUDA(cudaStreamWaitEvent(sd->st[k], sd->fork, 0));
+  }
   // ---- tails
   for (int i = 0; i < nt; ++i) {
+    const int c = i + 1;
+    cudaStream_t ts = tail_st(i);
     const int* cnt = f.counts + i;
     const int* rows = f.tail_rows + static_cast<long>(i) * N;
     const int ncols = a.cuts.cut[i + 1] - a.cuts.cut[i];
-    TNT_TRY(gather_rows(x, ldx, rows, cnt, N, f.xc, d, d, dt, 0, 0, st));
-    TNT_TRY(tail_proj(a, i, f.xc, d, N, cnt, f.proj, st));
+    // stale rows of the gather / projection buffers must be finite (0 x NaN inside a 64-row reduction block)
+    TNT_CUDA(cudaMemsetAsync(w.xc[c], 0, E * N * d, ts));
+    TNT_CUDA(cudaMemsetAsync(w.proj[c], 0, E * N * d, ts));
+    TNT_TRY(gather_rows(x, ldx, rows, cnt, N, w.xc[c], d, d, dt, 0, 0, ts));
+    TNT_TRY(tail_proj(a, i, w.xc[c], d, N, cnt, w.proj[c], ts));
     TNT_TRY(smgrad_rows_tail(f.tail_stats + static_cast<long>(i) * N, f.tail_loc + static_cast<long>(i) * N, cnt, N,
-                             row_w ? -1 : pad, w.row_lse, w.row_tgt, st));
+                             row_w ? -1 : pad, w.row_lse[c], w.row_tgt[c], ts));
+    LseExtra ex = {w.row_tgt[c], nullptr, 0, nullptr, 0, w.row_lse[c], gscale};
     if (row_w) {
-      TNT_TRY(gather_floats(row_w, rows, cnt, N, w.row_w, st));
-      ex.row_w = w.row_w;
+      TNT_TRY(gather_floats(row_w, rows, cnt, N, w.row_w[c], ts));
+      ex.row_w = w.row_w[c];
     }
-    TNT_TRY(gemm_call(f.proj, d, a.out_w[i], d, w.dz, w.ldz, N, ncols, d, dt, dt, TNT_NT, EPI_SMGRAD, cnt, nullptr, 0, &ex, st));
-    TNT_TRY(gemm_call(w.dz, w.ldz, a.out_w[i], d, w.dact, d, N, d, ncols, dt, dt, TNT_NN, EPI_NONE, cnt, nullptr, 0, nullptr, st));
-    TNT_TRY(gemm_call(w.dz, w.ldz, f.proj, d, d_out[i], d, ncols, d, N, dt, TNT_F32, TNT_TN, EPI_NONE, cnt, nullptr, 0, nullptr, st));
-    TNT_TRY(gemm_call(w.dact, d, a.proj_w[i], d, w.dxc, d, N, d, d, dt, dt, TNT_NN, EPI_NONE, cnt, nullptr, 0, nullptr, st));
-    TNT_TRY(gemm_call(w.dact, d, f.xc, d, d_proj[i], d, d, d, N, dt, TNT_F32, TNT_TN, EPI_NONE, cnt, nullptr, 0, nullptr, st));
-    TNT_TRY(scatter_add_rows(w.dxc, d, rows, cnt, N, dX, lddx, d, dt, 0, 0, st));
+    TNT_TRY(gemm_call(w.proj[c], d, a.out_w[i], d, w.dz[c], w.ldz[c], N, ncols, d, dt, dt, TNT_NT, EPI_SMGRAD, cnt, nullptr, 0, &ex, ts));
+    TNT_TRY(gemm_call(w.dz[c], w.ldz[c], a.out_w[i], d, w.dact[c], d, N, d, ncols, dt, dt, TNT_NN, EPI_NONE, cnt, nullptr, 0, nullptr, ts));
+    TNT_TRY(gemm_call(w.dact[c], d, a.proj_w[i], d, w.dxc[c], d, N, d, d, dt, dt, TNT_NN, EPI_NONE, cnt, nullptr, 0, nullptr, ts));
+    if (par) TNT_CUDA(cudaEventRecord(sd->done[i], ts));
+    TNT_TRY(gemm_call(w.dz[c], w.ldz[c], w.proj[c], d, d_out[i], d, ncols, d, N, dt, TNT_F32, TNT_TN, EPI_NONE, cnt, nullptr, 0, nullptr, ts));
+    TNT_TRY(gemm_call(w.dact[c], d, w.xc[c], d, d_proj[i], d, d, d, N, dt, TNT_F32, TNT_TN, EPI_NONE, cnt, nullptr, 0, nullptr, ts));
+  }
+  // ---- head cluster (st); its weight gradient on a lent stream
+  TNT_TRY(smgrad_rows_head(f.head_stats, f.side, f.head_t, N, nt, a.cuts.cut[0], pad, w.row_lse[0], w.row_tgt[0], st));
+  LseExtra ex = {w.row_tgt[0], nullptr, 0, nullptr, 0, w.row_lse[0], gscale};
+  ex.row_w = row_w;
+  TNT_TRY(gemm_call(x, ldx, a.head_w, d, w.dz[0], w.ldz[0], N, nh, d, dt, dt, TNT_NT, EPI_SMGRAD, nullptr, nullptr, 0, &ex, st));
+  if (par) {
+    TNT_CUDA(cudaEventRecord(sd->fork, st));
+    TNT_CUDA(cudaStreamWaitEvent(head_wst, sd->fork, 0));
+  }
+  TNT_TRY(gemm_call(w.dz[0], w.ldz[0], x, ldx, w.dhead, d, nh, d, N, dt, TNT_F32, TNT_TN, EPI_NONE, nullptr, nullptr, 0, nullptr, head_wst));
+  TNT_CUDA(cudaMemcpyAsync(d_head_words, w.dhead, sizeof(float) * a.cuts.cut[0] * d, cudaMemcpyDeviceToDevice, head_wst));
+  if (nt > 0)
+    TNT_CUDA(cudaMemcpyAsync(d_class_proj, w.dhead + static_cast<size_t>(a.cuts.cut[0]) * d, sizeof(float) * nt * d,
+                             cudaMemcpyDeviceToDevice, head_wst));
+  TNT_TRY(gemm_call(w.dz[0], w.ldz[0], a.head_w, d, dX, lddx, N, d, nh, dt, dt, TNT_NN, EPI_NONE, nullptr, nullptr, 0, nullptr, st));
+  // ---- the tails' rows join dX (in cluster order: the sums do not depend on the streams' timing)
+  for (int i = 0; i < nt; ++i) {
+    if (par) TNT_CUDA(cudaStreamWaitEvent(st, sd->done[i], 0));
+    TNT_TRY(scatter_add_rows(w.dxc[i + 1], d, f.tail_rows + static_cast<long>(i) * N, f.counts + i, N, dX, lddx, d, dt, 0, 0, st));
   }
   return TNT_OK;
 }

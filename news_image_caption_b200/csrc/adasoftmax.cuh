@@ -29,9 +29,13 @@ int adasoftmax_nll(const AdaSoftmax& a, const void* x, long ldx, const int64_t* 
 // dX [N, d] engine dtype (written), d_head_words [cut0, d], d_class_proj [n_tails, d], d_proj[i] [d, d],
 // d_out[i] [n_i, d]: fp32, written.
 size_t adasoftmax_bwd_workspace_bytes(const AdaSoftmax& a, int N);
+// streams lent by the caller: the clusters' chains and weight gradients spread over them.  On return st has every
+// contribution to dX; the parameter gradients are complete once the lent streams have drained (the caller joins them).
+struct AdaSide { int n; cudaStream_t st[4]; cudaEvent_t fork; cudaEvent_t done[TNT_MAX_CLUSTERS]; };
 int adasoftmax_nll_bwd(const AdaSoftmax& a, const void* x, long ldx, int N, int pad, float gscale, void* ws_fwd,
                        void* dX, long lddx, float* d_head_words, float* d_class_proj, float* const* d_proj,
-                       float* const* d_out, void* ws, size_t ws_bytes, cudaStream_t st, const float* row_w = nullptr);
+                       float* const* d_out, void* ws, size_t ws_bytes, cudaStream_t st, const float* row_w = nullptr,
+                       const AdaSide* sd = nullptr);
 // lp[r] = log softmax over the FULL vocabulary of target[r] (0 for pad targets); leaves the row statistics in `ws` for
 // adasoftmax_nll_bwd(..., row_w): the gradient of sum_r row_w[r] * (-lp[r])
 int adasoftmax_target_logprob(const AdaSoftmax& a, const void* x, long ldx, const int64_t* target, int N, int pad, float* lp,

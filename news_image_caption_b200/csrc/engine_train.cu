@@ -561,11 +561,11 @@ int step_setup(tnt_decoder* D, const tnt_contexts* ctx, void* workspace, size_t 
   if (want_side && !D->side_fork) {
     int lo = 0, hi = 0;
     TNT_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-    // measured (B = 64, one GPU, one side stream): highest priority 7.05 ms per step, lowest 7.12 ms -- the parameter-gradient
-    // kernels are short, and letting them in first keeps them from lingering beside three or four chain kernels
+    // measured (B = 64, one GPU): with ONE side stream the highest priority was better (7.05 vs 7.12 ms per step), with three
+    // the lowest is (6.57 vs 6.62 ms): the chain is the critical path, freed SMs go to its next kernel first
     const char* pe = getenv("TNT_SIDE_PRIO");
     for (int k = 0; k < want_side; ++k) {
-      TNT_CUDA(cudaStreamCreateWithPriority(&D->side_streams[k], cudaStreamNonBlocking, (pe && pe[0] == 'l') ? lo : hi));
+      TNT_CUDA(cudaStreamCreateWithPriority(&D->side_streams[k], cudaStreamNonBlocking, (pe && pe[0] == 'h') ? hi : lo));
       TNT_CUDA(cudaEventCreateWithFlags(&D->side_join[k], cudaEventDisableTiming));
     }
     TNT_CUDA(cudaStreamCreateWithFlags(&D->stage_stream, cudaStreamNonBlocking));
@@ -577,7 +577,7 @@ int step_setup(tnt_decoder* D, const tnt_contexts* ctx, void* workspace, size_t 
     TNT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     D->stage_events.push_back(e);
   }
-  while (static_cast<int>(D->side_layer_done.size()) < Ls * tnt_decoder::kSideStreams) {
+  while (static_cast<int>(D->side_layer_done.size()) < (Ls + 1) * tnt_decoder::kSideStreams) {
     cudaEvent_t e;
     TNT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     D->side_layer_done.push_back(e);
@@ -633,31 +633,46 @@ int train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, co
     d_out[i] = c.grad("embedder.token_embedder_adaptive.embeddings." + std::to_string(i + 1) + ".0.weight");
     TNT_CHECK_ARG(d_proj[i] && d_out[i], "decoder_train_step: gradient buffers of softmax tail %d missing", i);
   }
-  // ext: dz = row_w (onehot - p) = -row_w (p - onehot)
+  // stage `stage` is final when the chain AND the parameter-gradient work issued so far are: the event is recorded on a
+  // kernel-less stream that waits for both (neither the chain nor the side streams wait for each other here); `slot`
+  // = 0..Ls-1 after layer `slot`'s backward (those events also order the reuse of its PGradBufs), Ls after the loss
+  auto record_stage = [&](int stage, int slot) -> int {
+    if (!c.n_side) {
+      TNT_CUDA(cudaEventRecord(D->stage_events[stage], st));
+      return TNT_OK;
+    }
+    cudaStream_t s0 = D->stage_stream;
+    for (int k = 0; k < c.n_side; ++k) {
+      cudaEvent_t done = D->side_layer_done[slot * tnt_decoder::kSideStreams + k];
+      TNT_CUDA(cudaEventRecord(done, D->side_streams[k]));
+      TNT_CUDA(cudaStreamWaitEvent(s0, done, 0));
+    }
+    TNT_CUDA(cudaEventRecord(D->side_fork, st));
+    TNT_CUDA(cudaStreamWaitEvent(s0, D->side_fork, 0));
+    TNT_CUDA(cudaEventRecord(D->stage_events[stage], s0));
+    return TNT_OK;
+  };
+  // the clusters of the loss backward spread over the parameter-gradient streams (adasoftmax.cu); ext: dz = row_w (onehot - p)
+  AdaSide sd = {};
+  static const bool loss_par = !(getenv("TNT_LOSS_BWD_STREAMS") && atoi(getenv("TNT_LOSS_BWD_STREAMS")) == 0);
+  if (c.n_side && loss_par) {
+    sd.n = std::min(c.n_side, 4);
+    for (int k = 0; k < sd.n; ++k) sd.st[k] = D->side_streams[k];
+    sd.fork = D->side_fork;
+    for (int i = 0; i < nt && i < tnt_decoder::kSideStreams; ++i) sd.done[i] = D->side_join[i];
+    if (nt > tnt_decoder::kSideStreams) sd.n = 0;
+    c.side_pending = sd.n > 0;
+  }
   TNT_TRY(adasoftmax_nll_bwd(D->ada, w.Xbt, d, N, cf.pad_idx, ext ? -1.f : loss_scale, w.loss_fwd, w.dXbt, d, d_words, d_class,
-                             d_proj, d_out, w.loss_bwd, w.loss_bwd_bytes, st, ext ? ext->row_w : nullptr));
+                             d_proj, d_out, w.loss_bwd, w.loss_bwd_bytes, st, ext ? ext->row_w : nullptr, sd.n ? &sd : nullptr));
   if (ext && ext->dX) TNT_TRY(add_col_blocks(w.dXbt, d, ext->dX, d, N, d, 0, 1, cf.dtype, st));
   TNT_TRY(permute_rows(w.dXbt, w.gA, B, T, d, cf.dtype, true, st));                    // B x T -> T x B rows
   // ---------------- backward: layers, K/V projections, embedding
-  TNT_CUDA(cudaEventRecord(D->stage_events[0], st));
+  TNT_TRY(record_stage(0, Ls));
   for (int l = Ls - 1; l >= 0; --l) {
     const void* xin = l == 0 ? w.emb : w.act[l - 1].Xout;
     TNT_TRY(layer_bwd(c, ctx, w, l, xin, (ext && l == Ls - 1) ? ext->dattn : nullptr));
-    // stage Ls - l is final when the chain AND the parameter-gradient work of layer l are: the event is recorded on a
-    // kernel-less stream that waits for both (neither the chain nor the side streams wait for each other here)
-    if (c.n_side) {
-      cudaStream_t s0 = D->stage_stream;
-      for (int k = 0; k < c.n_side; ++k) {
-        cudaEvent_t done = D->side_layer_done[l * tnt_decoder::kSideStreams + k];
-        TNT_CUDA(cudaEventRecord(done, D->side_streams[k]));
-        TNT_CUDA(cudaStreamWaitEvent(s0, done, 0));
-      }
-      TNT_CUDA(cudaEventRecord(D->side_fork, st));
-      TNT_CUDA(cudaStreamWaitEvent(s0, D->side_fork, 0));
-      TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], s0));
-    } else {
-      TNT_CUDA(cudaEventRecord(D->stage_events[Ls - l], st));
-    }
+    TNT_TRY(record_stage(Ls - l, l));
   }
   const tnt_dropout d_emb = drop_site(dr, dr ? dr->dropout : 0.f, TNT_DROP_SITE_EMBED);
   if (d_emb.p > 0.f) TNT_TRY(dropout_apply(w.gA, d, nullptr, 0, w.gA, d, N, d, cf.dtype, d_emb, st));
@@ -665,6 +680,9 @@ int train_backward(tnt_decoder* D, const int64_t* ids, const int64_t* target, co
     TNT_TRY(permute_rows(ext->demb, w.gB, B, T, d, cf.dtype, true, st));
     TNT_TRY(add_col_blocks(w.gA, d, w.gB, d, N, d, 0, 1, cf.dtype, st));
   }
+  // the band tables are tied to the softmax output rows: embed_bwd ADDS its rows to what the loss backward's weight-gradient
+  // GEMMs (side streams) wrote -- stage 0 is long final by now, the wait only states the order
+  if (c.n_side) TNT_CUDA(cudaStreamWaitEvent(st, D->stage_events[0], 0));
   TNT_TRY(embed_bwd(c, ids, B, T, w, w.gA));
   TNT_TRY(side_join(c));                         // the caller's stream has every gradient from here on
   TNT_CUDA(cudaEventRecord(D->stage_events[Ls + 1], st));
