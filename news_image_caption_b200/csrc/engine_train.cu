@@ -192,8 +192,18 @@ int side_join(Ctx& c) {
 }
 inline cudaStream_t pstream(Ctx& c) { return c.n_side ? c.D->side_streams[c.job] : c.st; }
 // weight-gradient GEMM (TN: reduction over the tokens) on the parameter-gradient stream
+// The grids (and tile shapes) of the side-stream GEMMs are sized for 64 SMs, so that a chain GEMM of 128 CTAs finds most
+// of its SMs free; the dynamic tile scheduler lets either kernel absorb what the other leaves.  Measured at B = 64:
+// all SMs 6.56 ms per step, 96: 6.51, 64: 6.38, 32: 6.50 (TNT_SIDE_SM_BUDGET = n, 0 = all)
+inline int side_sm_budget() {
+  static const int n = [] { const char* e = getenv("TNT_SIDE_SM_BUDGET"); return e ? atoi(e) : 64; }();
+  return n;
+}
 template <typename... Args>
-int wgemm(Ctx& c, Args... args) { return gemm_on(pstream(c), c.dt, TNT_TN, EPI_NONE, args...); }
+int wgemm(Ctx& c, Args... args) {
+  SmBudget budget(c.n_side ? side_sm_budget() : 0);
+  return gemm_on(pstream(c), c.dt, TNT_TN, EPI_NONE, args...);
+}
 
 // gradient of a GehringLinear: dWp [rows(prepared order), cols] fp32 -> weight_v / weight_g (or plain weight)
 int linear_param_grads(Ctx& c, const std::string& prefix, const float* dWp, int rows, int cols, bool glu) {
