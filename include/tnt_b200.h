@@ -599,13 +599,15 @@ typedef struct {
   float grad_scale;                /* host scalar, 0 means 1 */
   float max_grad_norm, lr, beta1, beta2, eps, weight_decay;
   int norms_ready;                 /* 1: seg_sq already holds this step's per-tensor sums of squares (tnt_grad_sqnorm) */
+  int max_ctas;                    /* > 0: grid cap -- a slice stepped beside the backward pass (trainer, stage-wise) must not
+                                      take every SM's thread slots from the latency-bound kernels it overlaps; 0 = fill the GPU */
 } tnt_adam_params;
 int tnt_bert_adam_step(const tnt_adam_params* p, tnt_stream stream);
 /* seg_sq[segment] += sum of squares of grads[first, first + n) (whole 64-element chunks): the norm pass of the step above,
  * callable per arena slice as soon as that slice's gradients are final (the trainer runs it stage by stage on a side
  * stream beside the backward pass; seg_sq must have been zeroed once per step). */
-int tnt_grad_sqnorm(const float* grads, const int* seg_of_chunk, float* seg_sq, int64_t first, int64_t n,
-                    tnt_stream stream);
+int tnt_grad_sqnorm(const float* grads, const int* seg_of_chunk, float* seg_sq, int64_t first, int64_t n, int max_ctas,
+                    tnt_stream stream);   /* max_ctas as in tnt_adam_params */
 
 /* torch.optim.Adam over flat fp32 arenas -- the optimizer of the final* scripts: Adam(betas=(0.9, 0.98), eps=1e-9) driven by
  * the Noam schedule rate(step) = factor * d_model^-0.5 * min(step^-0.5, step * warmup^-1.5)

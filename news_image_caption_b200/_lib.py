@@ -119,7 +119,7 @@ class XattnBwdParams(C.Structure):
 class AdamParams(C.Structure):
     _fields_ = [('params', vp), ('grads', vp), ('m', vp), ('v', vp), ('n', i64), ('seg_of_chunk', vp), ('seg_sq', vp),
                 ('n_segments', i32), ('grad_scale_dev', vp), ('grad_scale', f32), ('max_grad_norm', f32), ('lr', f32),
-                ('beta1', f32), ('beta2', f32), ('eps', f32), ('weight_decay', f32), ('norms_ready', i32)]
+                ('beta1', f32), ('beta2', f32), ('eps', f32), ('weight_decay', f32), ('norms_ready', i32), ('max_ctas', i32)]
 
 
 class LseParams(C.Structure):
@@ -161,7 +161,7 @@ _SIGS = {
     'tnt_layernorm_bwd': (i32, [C.POINTER(LayernormBwdParams), vp]),
     'tnt_lse_fwd_static': (i32, [C.POINTER(LseParams), vp]),
     'tnt_lse_fwd_static_max_bytes': (C.c_size_t, []),
-    'tnt_grad_sqnorm': (i32, [vp, vp, vp, i64, i64, vp]),
+    'tnt_grad_sqnorm': (i32, [vp, vp, vp, i64, i64, i32, vp]),
     'tnt_embed_fwd': (i32, [C.POINTER(EmbedParams), vp]),
     'tnt_context_mix': (i32, [C.POINTER(ContextMixParams), vp]),
     'tnt_nan_mask': (i32, [C.POINTER(NanMaskParams), vp]),

@@ -106,7 +106,8 @@ extern "C" int tnt_bert_adam_step(const tnt_adam_params* a, tnt_stream stream) {
   if (a->n == 0) return TNT_OK;
   cudaStream_t st = as_stream(stream);
   const long n_chunks = a->n / kChunk;
-  const int grid = static_cast<int>(std::min<long>((a->n / 4 + 255) / 256, 16L * num_sms()));
+  int grid = static_cast<int>(std::min<long>((a->n / 4 + 255) / 256, 16L * num_sms()));
+  if (a->max_ctas > 0) grid = std::min(grid, a->max_ctas);
   if (a->max_grad_norm > 0.f && !a->norms_ready) {
     TNT_CUDA(cudaMemsetAsync(a->seg_sq, 0, sizeof(float) * a->n_segments, st));
     seg_sqnorm_kernel<<<grid, 256, 0, st>>>(a->grads, 0, n_chunks, a->seg_of_chunk, a->seg_sq);
@@ -120,13 +121,14 @@ extern "C" int tnt_bert_adam_step(const tnt_adam_params* a, tnt_stream stream) {
 }
 
 extern "C" int tnt_grad_sqnorm(const float* grads, const int* seg_of_chunk, float* seg_sq, int64_t first, int64_t n,
-                               tnt_stream stream) {
+                               int max_ctas, tnt_stream stream) {
   using namespace tnt;
   TNT_CHECK_ARG(grads && seg_of_chunk && seg_sq && first >= 0 && n >= 0, "grad_sqnorm: bad arguments");
   TNT_CHECK_ARG(first % kChunk == 0 && n % kChunk == 0, "grad_sqnorm: the range must be whole 64-element chunks");
   TNT_CHECK_ALIGN(aligned16(grads), "grad_sqnorm: alignment");
   if (n == 0) return TNT_OK;
-  const int grid = static_cast<int>(std::min<long>((n / 4 + 255) / 256, 16L * num_sms()));
+  int grid = static_cast<int>(std::min<long>((n / 4 + 255) / 256, 16L * num_sms()));
+  if (max_ctas > 0) grid = std::min(grid, max_ctas);
   seg_sqnorm_kernel<<<grid, 256, 0, as_stream(stream)>>>(grads, first / kChunk, (first + n) / kChunk, seg_of_chunk, seg_sq);
   TNT_LAUNCHED();
   return TNT_OK;

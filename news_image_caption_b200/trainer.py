@@ -178,6 +178,19 @@ class Trainer:
         env = __import__('os').environ.get('TNT_STAGE_NORMS')
         self.stage_norms = max_grad_norm > 0 and (env == '1' or (env is None and self.exchange.world > 1))
         self.norm_stream = torch.cuda.Stream() if (self.stage_norms and self.exchange.world == 1) else None
+        # BertAdam clips PER TENSOR, so a stage's tensors can be stepped as soon as that stage's gradients (and norms) are
+        # final: slice by slice behind the stage events -- on the communication stream right behind the slice's all-reduce
+        # (or on a side stream on one GPU).  What stays in the step's tail: the slices that are only final when the backward
+        # ends (the tied band tables: a third of the parameters).  Measured: 2 GPUs 7.05 -> 6.97 ms per step; ONE GPU 6.39 ->
+        # 6.39..6.44 ms (the HBM-bound update slows the backward it overlaps by as much as it saves; with a small grid --
+        # TNT_ADAM_BG_CTAS -- it becomes the tail itself: 6.69 ms at 148 CTAs), so it is on for world > 1 only
+        # (TNT_STAGE_ADAM=0 / 1 overrides).
+        env_sa = __import__('os').environ.get('TNT_STAGE_ADAM')
+        self.stage_adam = overlap and (env_sa == '1' or (env_sa is None and self.exchange.world > 1))
+        self.bg_ctas = int(__import__('os').environ.get('TNT_ADAM_BG_CTAS', '0'))
+        if self.stage_adam and self.exchange.world == 1:
+            self.stage_norms = max_grad_norm > 0
+            self.norm_stream = torch.cuda.Stream()
         # multi-GPU: the embedding rows of the tied band tables travel as a packed list (the arena keeps the band tables in
         # stage 0, where their dense softmax part is final); a band whose dim differs from d keeps the dense path
         self.sparse = None
@@ -239,20 +252,58 @@ class Trainer:
             order, wait_on = list(range(n_stages)), {}
         late = []                               # slices whose norms can only be summed on the step's stream, at the end
 
-        def sqnorm(s, stream):
+        def sqnorm(s, stream, max_ctas=0):
             a, b = self.exchange.slices[s]
             if a is not None and b > a:
                 _lib.check(L.tnt_grad_sqnorm(C.c_void_p(dec.flat_grads.data_ptr()), C.c_void_p(self.seg_of_chunk.data_ptr()),
-                                             C.c_void_p(self.seg_sq.data_ptr()), a, b - a, C.c_void_p(stream.cuda_stream)),
+                                             C.c_void_p(self.seg_sq.data_ptr()), a, b - a, max_ctas, C.c_void_p(stream.cuda_stream)),
                            'tnt_grad_sqnorm')
-        if self.exchange.world == 1 and stage_norms:
+        done = set()                            # slices BertAdam has already stepped (stage-wise)
+        ln2 = math.log(2.0)
+
+        def gscale_now():
+            # gradient of the reference loss (sum-NLL / n_tokens / ln 2): scale by the global token count on the device
+            # (an all-padding global batch has n_tokens == 0: every gradient is 0 then, keep the scale finite)
+            torch.reciprocal(out[1:2].clamp_min(1.0) * ln2, out=self.gscale)
+
+        bg = self.bg_ctas                       # grid cap of the passes that run beside the backward
+
+        def adam(stream, s=None, max_ctas=0):
+            a = _lib.AdamParams()
+            a.max_ctas = max_ctas
+            lo, n = 0, dec.flat_params.numel()
+            if s is not None:
+                lo, hi = self.exchange.slices[s]
+                if lo is None or hi <= lo:
+                    return
+                n = hi - lo
+            a.params, a.grads = dec.flat_params.data_ptr() + 4 * lo, dec.flat_grads.data_ptr() + 4 * lo
+            a.m, a.v = self.m.data_ptr() + 4 * lo, self.v.data_ptr() + 4 * lo
+            a.n = n
+            a.seg_of_chunk, a.seg_sq, a.n_segments = self.seg_of_chunk.data_ptr() + 4 * (lo // 64), self.seg_sq.data_ptr(), self.n_segments
+            a.grad_scale_dev, a.grad_scale = self.gscale.data_ptr(), 1.0
+            a.max_grad_norm, a.lr = self.max_norm, self.lr_now()
+            a.beta1, a.beta2, a.eps, a.weight_decay = self.betas[0], self.betas[1], self.eps, self.wd
+            a.norms_ready = 1 if (stage_norms or self.max_norm <= 0) else 0
+            _lib.check(L.tnt_bert_adam_step(C.byref(a), C.c_void_p(stream.cuda_stream)), 'tnt_bert_adam_step')
+
+        if self.exchange.world == 1 and (stage_norms or self.stage_adam):
             if self.norm_stream is None:
                 self.norm_stream = torch.cuda.Stream()
             ns = self.norm_stream
-            for s in order:                     # the stage events order this after seg_sq.zero_() too
+            out.record_stream(ns)
+            for j, s in enumerate(order):       # the stage events order this after seg_sq.zero_() too
                 _lib.check(L.tnt_decoder_stream_wait_stage(h, wait_on.get(s, s), C.c_void_p(ns.cuda_stream)),
                            'tnt_decoder_stream_wait_stage')
-                sqnorm(s, ns)
+                last = j == len(order) - 1      # nothing left to overlap with: full width
+                if stage_norms:
+                    sqnorm(s, ns, 0 if last else bg)
+                if self.stage_adam:
+                    if j == 0:
+                        with torch.cuda.stream(ns):
+                            gscale_now()        # (loss_sum, n_tokens) exist before any stage event
+                    adam(ns, s, 0 if last else bg)
+                    done.add(s)
             cur.wait_stream(ns)
         if self.exchange.world > 1:
             if self.overlap:
@@ -262,12 +313,18 @@ class Trainer:
                                    'tnt_decoder_stream_wait_stage')
                         if j == 0:      # (loss_sum, n_tokens) exist once the forward has ended: exchanged here, off the step's tail
                             self.exchange.reduce_scalars(out)
+                            if self.stage_adam:
+                                out.record_stream(self.comm_stream)
+                                gscale_now()
                         self.exchange.reduce_slice(s)
+                        if s == 0 and self.sparse is not None:
+                            late.append(s)              # the band tables still get the gathered embedding rows
+                            continue
                         if stage_norms:
-                            if s == 0 and self.sparse is not None:
-                                late.append(s)          # the band tables still get the gathered embedding rows
-                            else:
-                                sqnorm(s, self.comm_stream)
+                            sqnorm(s, self.comm_stream, bg if self.stage_adam else 0)
+                        if self.stage_adam and (stage_norms or self.max_norm <= 0):
+                            adam(self.comm_stream, s, bg)
+                            done.add(s)
                     if self.sparse is not None:
                         self.sparse.gather()
                     self.exchange.finish()
@@ -281,19 +338,15 @@ class Trainer:
             if self.sparse is not None:
                 self.sparse.scatter_into(dec.band_table_grads(), dec.embed_padding_idx)
             for s in late:
-                sqnorm(s, cur)
-        # gradient of the reference loss (sum-NLL / n_tokens / ln 2): scale by the global token count on the device
-        # (an all-padding global batch has n_tokens == 0: every gradient is 0 then, keep the scale finite)
-        torch.reciprocal(out[1:2].clamp_min(1.0) * math.log(2.0), out=self.gscale)
-        a = _lib.AdamParams()
-        a.params, a.grads, a.m, a.v = dec.flat_params.data_ptr(), dec.flat_grads.data_ptr(), self.m.data_ptr(), self.v.data_ptr()
-        a.n = dec.flat_params.numel()
-        a.seg_of_chunk, a.seg_sq, a.n_segments = self.seg_of_chunk.data_ptr(), self.seg_sq.data_ptr(), self.n_segments
-        a.grad_scale_dev, a.grad_scale = self.gscale.data_ptr(), 1.0
-        a.max_grad_norm, a.lr = self.max_norm, self.lr_now()
-        a.beta1, a.beta2, a.eps, a.weight_decay = self.betas[0], self.betas[1], self.eps, self.wd
-        a.norms_ready = 1 if stage_norms else 0
-        _lib.check(L.tnt_bert_adam_step(C.byref(a), C.c_void_p(cur.cuda_stream)), 'tnt_bert_adam_step')
+                if stage_norms:
+                    sqnorm(s, cur)
+        if not done:
+            gscale_now()
+            adam(cur)                           # the whole arena in one pass
+        else:
+            for s in range(len(self.exchange.slices)):
+                if s not in done:
+                    adam(cur, s)
         self.step_no += 1
         dec.mark_updated()
         return out
