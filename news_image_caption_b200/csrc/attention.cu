@@ -257,8 +257,12 @@ bool xattn_step_supported(const tnt_xattn_params* p);
 int xattn_fwd_step(const tnt_xattn_params* p, cudaStream_t st);
 static bool g_force_simt_attn = false;
 bool xattn_force_simt() { return g_force_simt_attn; }
+bool xattn_short_supported(const tnt_xattn_params* p);                                  // attention_short.cu
+int xattn_short_multi(const tnt_xattn_params* ps, int n, cudaStream_t st);
+
 int xattn_fwd_dispatch(const tnt_xattn_params* p, cudaStream_t st) {
   if (!g_force_simt_attn && xattn_step_supported(p)) return xattn_fwd_step(p, st);      // T == 1: HBM-streaming decode kernel
+  if (!g_force_simt_attn && xattn_short_supported(p)) return xattn_short_multi(p, 1, st);   // <= 128 keys: warp-level mma kernel
   if (!g_force_simt_attn && xattn_tc_supported(p)) {
     variant_hit(V_XATTN_TC);
     if (p->tile_live) variant_hit(V_XATTN_TC_TILESKIP);

@@ -16,7 +16,7 @@ void count_launch(int n = 1);
 // the one the parity tests exercised (CTA-pair GEMM, split-K plan, tile-skipping attention, ...)
 enum Variant {
   V_GEMM_TC_1CTA, V_GEMM_TC_PAIR, V_GEMM_SPLITK, V_GEMM_SIMT,
-  V_XATTN_TC, V_XATTN_TC_TILESKIP, V_XATTN_TC_WEIGHTS, V_XATTN_SIMT, V_XATTN_STEP,
+  V_XATTN_TC, V_XATTN_TC_TILESKIP, V_XATTN_TC_WEIGHTS, V_XATTN_SIMT, V_XATTN_STEP, V_XATTN_SHORT,
   V_XATTN_BWD_TC, V_XATTN_BWD_SIMT,
   V_DYNCONV_FWD_TC, V_DYNCONV_FWD_SIMT, V_DYNCONV_BWD_TC, V_DYNCONV_BWD_SIMT, V_DYNCONV_STEP_FAST, V_DYNCONV_STEP_SIMT,
   V_LN_GEMM_FUSED, V_COUNT

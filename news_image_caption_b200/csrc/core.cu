@@ -32,7 +32,7 @@ bool pdl_enabled() {
 static std::atomic<uint64_t> g_variants[V_COUNT];
 static const char* const kVariantNames[V_COUNT] = {
     "gemm.tc.1cta", "gemm.tc.pair", "gemm.splitk", "gemm.simt",
-    "xattn.tc", "xattn.tc.tileskip", "xattn.tc.weights", "xattn.simt", "xattn.step",
+    "xattn.tc", "xattn.tc.tileskip", "xattn.tc.weights", "xattn.simt", "xattn.step", "xattn.short",
     "xattn_bwd.tc", "xattn_bwd.simt",
     "dynconv.fwd.tc", "dynconv.fwd.simt", "dynconv.bwd.tc", "dynconv.bwd.simt", "dynconv.step.fast", "dynconv.step.simt",
     "gemm.ln_fused"};

@@ -14,6 +14,8 @@ int xattn_fwd_step_multi(const tnt_xattn_params* ps, int n, cudaStream_t st, int
                          float* scores = nullptr, int scores_src = -1, float* weights_out = nullptr);
 int xattn_live_order(const uint32_t* tile_live, int B, int* order, cudaStream_t st);
 bool xattn_force_simt();
+bool xattn_short_supported(const tnt_xattn_params* p);
+int xattn_short_multi(const tnt_xattn_params* ps, int n, cudaStream_t st);
 
 namespace {
 inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
@@ -303,7 +305,21 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
                                  sw ? attn_out : nullptr));   // decode step: every source of the layer in one launch
     prof_end(pid, st);
   } else {
+    // the short sources of the layer (image regions, faces, objects: <= 128 keys) share ONE launch of the warp-level kernel
+    tnt_xattn_params shorts[TNT_MAX_SOURCES];
+    bool is_short[TNT_MAX_SOURCES] = {};
+    int n_short = 0;
     for (int s = 0; s < ns; ++s) {
+      is_short[s] = !xattn_force_simt() && xattn_short_supported(&aps[s]);
+      if (is_short[s]) shorts[n_short++] = aps[s];
+    }
+    if (n_short) {
+      const int pid = prof_enabled() ? prof_begin("xattn.short", st) : -1;
+      TNT_TRY(xattn_short_multi(shorts, n_short, st));
+      prof_end(pid, st);
+    }
+    for (int s = 0; s < ns; ++s) {
+      if (is_short[s]) continue;
       const tnt_xattn_params& ap = aps[s];
       int pid = -1;
       if (prof_enabled()) {

@@ -32,7 +32,7 @@ def variants():
     from news_image_caption_b200 import _lib
     L = _lib.lib()
     names = ['gemm.tc.1cta', 'gemm.tc.pair', 'gemm.splitk', 'gemm.simt', 'xattn.tc', 'xattn.tc.tileskip', 'xattn.tc.weights',
-             'xattn.simt', 'xattn.step', 'xattn_bwd.tc', 'xattn_bwd.simt', 'dynconv.fwd.tc', 'dynconv.fwd.simt',
+             'xattn.simt', 'xattn.step', 'xattn.short', 'xattn_bwd.tc', 'xattn_bwd.simt', 'dynconv.fwd.tc', 'dynconv.fwd.simt',
              'dynconv.bwd.tc', 'dynconv.bwd.simt', 'dynconv.step.fast', 'dynconv.step.simt']
     return {n: L.tnt_variant_count(n.encode()) for n in names}
 
@@ -122,7 +122,9 @@ def test_c2_forward_B64_sampled_rows(models, need_attn):
     v = _forward_case(models, '2src', 64, need_attn)
     assert v['gemm.tc.pair'] >= 2            # the image and article K/V projections take the cta_group::2 kernel at this size
     assert v['gemm.simt'] == 0 and v['xattn.simt'] == 0, v      # no fp32 SIMT fallback anywhere in the default bf16 path
-    assert v['xattn.tc'] == 8 and v['xattn.tc.tileskip'] == 8   # 4 layers x 2 sources, both carry a key-padding mask: live-tile lists on
+    # 4 layers: the article on the tcgen05 kernel (key-padding mask: live-tile lists on), the image regions (51 keys) on the
+    # warp-level kernel for short sources
+    assert v['xattn.tc'] == 4 and v['xattn.tc.tileskip'] == 4 and v['xattn.short'] == 4
     assert v['xattn.tc.weights'] == (1 if need_attn else 0)     # the last layer's article attention returns its weights
     assert v['dynconv.fwd.tc'] == 4 and v['dynconv.fwd.simt'] == 0
 
@@ -132,7 +134,8 @@ def test_c4_forward_B128_four_sources_sampled_rows(models):
     v = _forward_case(models, '4src', 128, True)
     assert v['gemm.tc.pair'] >= 3
     assert v['gemm.simt'] == 0 and v['xattn.simt'] == 0, v
-    assert v['xattn.tc'] == 16 and v['xattn.tc.weights'] == 1
+    assert v['xattn.tc'] == 4 and v['xattn.tc.weights'] == 1     # the article; image + faces + objects share ONE short-source
+    assert v['xattn.short'] == 4                                  # launch per layer
 
 
 def test_c5_generation_B256_bf16_sampled_rows(models):

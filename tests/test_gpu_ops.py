@@ -421,6 +421,48 @@ def test_xattn_tcgen05(ops, T, B, S):
     assert rel_err(o, o2) < 1.5e-2
 
 
+@pytest.mark.parametrize('T,B,S', [(32, 3, 51), (32, 5, 6), (40, 2, 66), (9, 2, 128), (2, 3, 17), (33, 2, 100)])
+def test_xattn_short_sources(ops, T, B, S):
+    """Warp-level mma kernel for memory sources of <= 128 keys (attention_short.cu; image regions / faces / objects): output,
+    LSE and the dropped-out probabilities vs a plain fp32 torch reference and vs the SIMT kernel (same dropout stream)."""
+    from news_image_caption_b200 import _lib
+    L = _lib.lib()
+    g = torch.Generator().manual_seed(T * 1000 + S)
+    E, H = 1024, 16
+    q = torch.randn(T, B, E, generator=g).bfloat16()
+    k = torch.randn(S, B, E, generator=g).bfloat16()
+    v = torch.randn(S, B, E, generator=g).bfloat16()
+    n = torch.randint(0, max(S - 2, 1), (B,), generator=g)
+    n[0] = S - 2
+    mask = torch.arange(S - 2)[None] >= n[:, None]                      # [B, S-2]; last two keys never masked
+    full = torch.cat([mask, torch.zeros(B, 2, dtype=torch.bool)], 1)
+    qh = q.float().view(T, B, H, 64).permute(1, 2, 0, 3) * 0.125
+    kh = k.float().view(S, B, H, 64).permute(1, 2, 0, 3)
+    vh = v.float().view(S, B, H, 64).permute(1, 2, 0, 3)
+    s = (qh @ kh.transpose(-1, -2)).masked_fill(full[:, None, None, :], float('-inf'))
+    ref = (torch.softmax(s, -1) @ vh).permute(2, 0, 1, 3).reshape(T, B, E)
+    lse_ref = torch.logsumexp(s, -1)                                    # [B, H, T]
+    n0 = L.tnt_variant_count(b'xattn.short')
+    lse = torch.zeros(B, H, T, device='cuda')
+    o, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, 0.125, pad_mask=mask.cuda(), mask_S=S - 2, lse=lse)
+    torch.cuda.synchronize()
+    assert L.tnt_variant_count(b'xattn.short') == n0 + 1
+    assert rel_err(o, ref) < 2e-2
+    assert (lse.cpu() - lse_ref).abs().max().item() < 2e-2
+    # dropout on the probabilities: same counter-based mask as the SIMT kernel
+    drop = (0.3, 1234, 77)
+    od, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, 0.125, pad_mask=mask.cuda(), mask_S=S - 2, drop=drop)
+    L.tnt_debug_force_simt_attention(1)
+    try:
+        o2, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, 0.125, pad_mask=mask.cuda(), mask_S=S - 2)
+        od2, _ = ops.xattn(q.cuda(), k.cuda(), v.cuda(), H, 0.125, pad_mask=mask.cuda(), mask_S=S - 2, drop=drop)
+    finally:
+        L.tnt_debug_force_simt_attention(0)
+    assert rel_err(o, o2) < 1.5e-2
+    assert rel_err(od, od2) < 2e-2
+    assert rel_err(od, o) > 5e-2                                        # the mask did something
+
+
 def test_xattn_v2_causal(ops):
     """final*/transformer_v2 attention(): mask == 0 -> -1e9, causal self-attention, d_k = 128."""
     g = torch.Generator().manual_seed(8)

@@ -29,8 +29,12 @@ def main():
     ap.add_argument('--workload', default='fwd', choices=sorted(bench.WORKLOADS))
     ap.add_argument('--out', default=None)
     ap.add_argument('--max-lines', type=int, default=500)
+    ap.add_argument('--simt-attention', action='store_true', help='force the SIMT attention kernels (diagnosis)')
     a = ap.parse_args()
     w = bench.WORKLOADS[a.workload]
+    if a.simt_attention:
+        from news_image_caption_b200 import _lib
+        _lib.lib().tnt_debug_force_simt_attention(1)
     sd = random_state_dict(seed=0, sources=w['sources'])
     dec = DynamicConvDecoder(sources=w['sources'], dtype=torch.bfloat16).load_reference_state_dict(sd)
     prev, tgt, ctx = bench.make_inputs(a.workload, 1234)
