@@ -82,6 +82,8 @@ struct tnt_decoder {
   tnt_dropout_config pending_drc = {}; bool pending_dr_on = false; void* pending_ws = nullptr;   // train_forward -> train_backward
   // pipelined host scoring (tnt_decoder_score_host_submit / _wait): copy stream + per-slot events
   cudaStream_t copy_stream = nullptr;
+  cudaStream_t copy_extra[3] = {};         // further DMA queues of the live-row copies (TNT_H2D_STREAMS, default 2 in all)
+  cudaEvent_t ev_cx_fork = nullptr, ev_cx_join[3] = {};
   cudaEvent_t ev_h2d[2] = {}, ev_free[2] = {}, ev_done[2] = {};
   bool slot_used[2] = {false, false};
   std::set<const void*> zeroed_staging;    // staging memory regions whose skipped (padded) rows have been zeroed once

@@ -342,6 +342,53 @@ Staging carve_staging(const tnt_decoder* D, int B, int T, const int* S, void* ba
 // (width = one E-element row, height = len_b, pitch = B rows) -- the padded tail of an article (mean live length ~ 320 of
 // 512) is never read by any kernel (a masked key contributes exactly 0), so it need not cross PCIe.  The staging rows that
 // are skipped keep stale but FINITE values: the buffer is zeroed the first time this decoder sees it.
+// Live-row host -> device copy as ONE kernel that reads the pinned host tensor over PCIe itself (zero copy): CTA = caption b,
+// len_b found from the caption's key-padding bytes (also read from the host), rows s < len_b fetched with 16-byte loads (a
+// warp per row, 4 chunks per lane in flight) and stored to the device layout.  The DMA-engine form is one strided 2-D copy
+// per caption and source: 132 copies per step at B = 64, each with ~3.5 us of fixed cost -- a quarter of the copy engine's
+// time (tools/trace_e2e.py), which made the host-buffer path copy-bound on boxes with a slow PCIe link.
+__global__ void __launch_bounds__(256) h2d_live_rows_kernel(uint4* dst, const uint4* src, const uint8_t* mask, int S, int B,
+                                                            int row16 /* 16-byte chunks per row */) {
+  __shared__ int s_len;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    if (threadIdx.x == 0) s_len = 0;
+    __syncthreads();
+    int last = 0;                                    // 1 + the last un-masked position this thread saw
+    for (int i = threadIdx.x; i < S; i += 256)
+      if (mask[static_cast<size_t>(b) * S + i] == 0) last = i + 1;
+    if (last) atomicMax(&s_len, last);
+    __syncthreads();
+    const int len = s_len;
+    const size_t pitch16 = static_cast<size_t>(B) * row16;
+    for (int r = warp; r < len; r += 8) {
+      const uint4* sp = src + r * pitch16 + static_cast<size_t>(b) * row16;
+      uint4* dp = dst + r * pitch16 + static_cast<size_t>(b) * row16;
+      for (int c0 = lane; c0 < row16; c0 += 128) {
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (c0 + 32 * u < row16) v[u] = sp[c0 + 32 * u];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (c0 + 32 * u < row16) dp[c0 + 32 * u] = v[u];
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// device-visible aliases of pinned host pointers (UVA: normally the same address); false = not mapped, use the DMA path
+bool host_dev_ptr(const void* host, const void** dev) {
+  void* p = nullptr;
+  if (cudaHostGetDevicePointer(&p, const_cast<void*>(host), 0) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  *dev = p;
+  return true;
+}
+
 int h2d_source(tnt_decoder* D, void* dst, const void* src_host, const uint8_t* mask_host, int S, int B, int E, size_t esz,
                cudaStream_t st, size_t* bytes_out) {
   const size_t row = static_cast<size_t>(E) * esz, all = static_cast<size_t>(S) * B * row;
@@ -357,14 +404,56 @@ int h2d_source(tnt_decoder* D, void* dst, const void* src_host, const uint8_t* m
     D->zeroed_staging.insert(dst);
   }
   const size_t pitch = static_cast<size_t>(B) * row;
+  static const bool zero_copy = [] { const char* e = getenv("TNT_H2D_ZEROCOPY"); return e && e[0] == '1'; }();   // measured slower: off
+  const void *src_dev = nullptr, *mask_dev = nullptr;
+  if (zero_copy && row % 16 == 0 && aligned16(dst) && aligned16(src_host) && host_dev_ptr(src_host, &src_dev) &&
+      host_dev_ptr(mask_host, &mask_dev)) {
+    h2d_live_rows_kernel<<<std::min(B, 2 * num_sms()), 256, 0, st>>>(static_cast<uint4*>(dst), static_cast<const uint4*>(src_dev),
+                                                                     static_cast<const uint8_t*>(mask_dev), S, B,
+                                                                     static_cast<int>(row / 16));
+    TNT_LAUNCHED();
+    if (bytes_out) {
+      for (int b = 0; b < B; ++b) {
+        const uint8_t* m = mask_host + static_cast<size_t>(b) * S;
+        int len = S;
+        while (len > 0 && m[len - 1]) --len;
+        *bytes_out += row * len;
+      }
+    }
+    return TNT_OK;
+  }
+  // The captions' strided copies are dealt round-robin to TNT_H2D_STREAMS streams (default 2).  Beside a running forward
+  // pass one queue of 2-D copies drops to ~30 GB/s (tools/trace_e2e.py: 44 MB in 1.46 ms, the rest of the batch exposed);
+  // two queues: e2e step 1.78 -> 1.72 ms on a 33 GB/s box, 1.84 (2.9 in one run) -> 1.72 ms on a 55 GB/s box.
+  static const int n_q = [] { const char* e = getenv("TNT_H2D_STREAMS"); return e ? std::max(1, std::min(atoi(e), 4)) : 2; }();
+  cudaStream_t q[4] = {st, st, st, st};
+  const int nq = D ? n_q : 1;
+  if (nq > 1) {
+    if (!D->ev_cx_fork) {
+      TNT_CUDA(cudaEventCreateWithFlags(&D->ev_cx_fork, cudaEventDisableTiming));
+      for (int i = 0; i < 3; ++i) {
+        TNT_CUDA(cudaStreamCreateWithFlags(&D->copy_extra[i], cudaStreamNonBlocking));
+        TNT_CUDA(cudaEventCreateWithFlags(&D->ev_cx_join[i], cudaEventDisableTiming));
+      }
+    }
+    TNT_CUDA(cudaEventRecord(D->ev_cx_fork, st));
+    for (int i = 1; i < nq; ++i) {
+      q[i] = D->copy_extra[i - 1];
+      TNT_CUDA(cudaStreamWaitEvent(q[i], D->ev_cx_fork, 0));
+    }
+  }
   for (int b = 0; b < B; ++b) {
     const uint8_t* m = mask_host + static_cast<size_t>(b) * S;
     int len = S;
     while (len > 0 && m[len - 1]) --len;
     if (!len) continue;
     TNT_CUDA(cudaMemcpy2DAsync(static_cast<char*>(dst) + b * row, pitch, static_cast<const char*>(src_host) + b * row, pitch, row, len,
-                               cudaMemcpyHostToDevice, st));
+                               cudaMemcpyHostToDevice, q[b % nq]));
     if (bytes_out) *bytes_out += row * len;
+  }
+  for (int i = 1; i < nq; ++i) {
+    TNT_CUDA(cudaEventRecord(D->ev_cx_join[i - 1], q[i]));
+    TNT_CUDA(cudaStreamWaitEvent(st, D->ev_cx_join[i - 1], 0));
   }
   return TNT_OK;
 }
@@ -491,6 +580,24 @@ extern "C" int64_t tnt_h2d_live_rows(void* dst, const void* src_host, const uint
   if (!mask_host) {
     if (cudaMemcpyAsync(dst, src_host, pitch * S, cudaMemcpyHostToDevice, st) != cudaSuccess) return TNT_ERR_CUDA;
     return static_cast<int64_t>(pitch * S);
+  }
+  {
+    static const bool zero_copy = [] { const char* e = getenv("TNT_H2D_ZEROCOPY"); return e && e[0] == '1'; }();   // measured slower: off
+    const void *src_dev = nullptr, *mask_dev = nullptr;
+    if (zero_copy && row % 16 == 0 && aligned16(dst) && aligned16(src_host) && host_dev_ptr(src_host, &src_dev) &&
+        host_dev_ptr(mask_host, &mask_dev)) {
+      h2d_live_rows_kernel<<<std::min(B, 2 * num_sms()), 256, 0, st>>>(static_cast<uint4*>(dst), static_cast<const uint4*>(src_dev),
+                                                                       static_cast<const uint8_t*>(mask_dev), S, B,
+                                                                       static_cast<int>(row / 16));
+      TNT_LAUNCHED();
+      for (int b = 0; b < B; ++b) {
+        const uint8_t* m = mask_host + static_cast<size_t>(b) * S;
+        int len = S;
+        while (len > 0 && m[len - 1]) --len;
+        bytes += static_cast<int64_t>(row) * len;
+      }
+      return bytes;
+    }
   }
   for (int b = 0; b < B; ++b) {
     const uint8_t* m = mask_host + static_cast<size_t>(b) * S;

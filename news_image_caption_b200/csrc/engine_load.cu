@@ -204,7 +204,27 @@ extern "C" tnt_decoder* tnt_decoder_create(const tnt_decoder_config* cfg) {
   return D;
 }
 
-extern "C" void tnt_decoder_destroy(tnt_decoder* d) { delete d; }
+extern "C" void tnt_decoder_destroy(tnt_decoder* d) {
+  if (!d) return;
+  // library-owned streams and events (cudaStreamDestroy lets queued work finish; the handles are released afterwards)
+  auto ev = [](cudaEvent_t& e) { if (e) cudaEventDestroy(e); e = nullptr; };
+  auto st = [](cudaStream_t& s) { if (s) cudaStreamDestroy(s); s = nullptr; };
+  for (cudaEvent_t& e : d->stage_events) ev(e);
+  for (cudaEvent_t& e : d->side_layer_done) ev(e);
+  for (cudaStream_t& s : d->side_streams) st(s);
+  for (cudaEvent_t& e : d->side_join) ev(e);
+  ev(d->side_fork);
+  st(d->stage_stream);
+  for (cudaStream_t& s : d->sub_streams) st(s);
+  for (cudaEvent_t& e : d->sub_join) ev(e);
+  ev(d->sub_fork);
+  st(d->copy_stream);
+  for (cudaStream_t& s : d->copy_extra) st(s);
+  for (cudaEvent_t& e : d->ev_cx_join) ev(e);
+  ev(d->ev_cx_fork);
+  for (int i = 0; i < 2; ++i) { ev(d->ev_h2d[i]); ev(d->ev_free[i]); ev(d->ev_done[i]); }
+  delete d;
+}
 
 extern "C" size_t tnt_decoder_weight_bytes(const tnt_decoder* d) { return d ? d->wbytes : 0; }
 
