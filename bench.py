@@ -469,19 +469,25 @@ def bench_forward(env, wl, dec, sd, args, with_sustained=False):
     # flight (submit step i+1, then wait for step i) so the copies of one batch overlap the compute of the other
     for _ in range(2):
         dec.score_host(prev_h, tgt_h, ctx_h)
-    sync_all(env)
-    t0 = time.perf_counter()
-    dec.score_host_submit(0, prev_h, tgt_h, ctx_h)
-    for i in range(1, args.steps):
-        dec.score_host_submit(i & 1, prev_h, tgt_h, ctx_h)
-        l_h, n_h = dec.score_host_wait((i - 1) & 1)
-    l_h, n_h = dec.score_host_wait((args.steps - 1) & 1)
-    e2e_s = all_max(env, time.perf_counter() - t0)
+    # K steps per repetition (pipeline fill included every time); the MEDIAN of 5 repetitions is reported: a 35 ms wall-clock
+    # region that includes PCIe traffic moved by 10 % from run to run on the same box (1.71 / 1.87 ms per step back to back)
+    reps = []
+    for _ in range(5):
+        sync_all(env)
+        t0 = time.perf_counter()
+        dec.score_host_submit(0, prev_h, tgt_h, ctx_h)
+        for i in range(1, args.steps):
+            dec.score_host_submit(i & 1, prev_h, tgt_h, ctx_h)
+            l_h, n_h = dec.score_host_wait((i - 1) & 1)
+        l_h, n_h = dec.score_host_wait((args.steps - 1) & 1)
+        reps.append(all_max(env, time.perf_counter() - t0))
+    e2e_s = sorted(reps)[len(reps) // 2]
     assert abs(l_h - loss_check[0].item()) < 1e-3 * abs(l_h) and int(n_h) == ntok, (l_h, loss_check, n_h, ntok)
     h2d_full, h2d = h2d, int(env.L.tnt_decoder_last_h2d_bytes(dec._h()))     # counted by the library from the copies it issued
     res['e2e'] = {'value': ntok_all * args.steps / e2e_s, 'unit': 'tokens/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 8,
                   'h2d_bytes_if_padding_were_copied': h2d_full,
-                  'captions_per_sec': B * env.world * args.steps / e2e_s, 'ms_per_step': 1e3 * e2e_s / args.steps}
+                  'captions_per_sec': B * env.world * args.steps / e2e_s, 'ms_per_step': 1e3 * e2e_s / args.steps,
+                  'repetitions_ms_per_step': [round(1e3 * r / args.steps, 4) for r in reps], 'reported': 'median of 5 repetitions of K steps'}
     if env.rank == 0:
         res['roofline'] = kv_roofline(B, t, ms_step)
         if not args.no_parity:
