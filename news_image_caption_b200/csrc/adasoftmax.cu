@@ -324,9 +324,10 @@ int adasoftmax_nll(const AdaSoftmax& a, const void* x, long ldx, const int64_t* 
                                                       w.tail_rows + static_cast<long>(i) * N, w.counts + i, a.d,
                                                       static_cast<float*>(w.xc));
     TNT_LAUNCHED();
-    TNT_TRY(tail_proj(a, i, w.xc, a.d, N, w.counts + i, w.proj, st));
+    const bool fold = a.use_fold && a.fold_w[i];
+    if (!fold) TNT_TRY(tail_proj(a, i, w.xc, a.d, N, w.counts + i, w.proj, st));
     const int ncols = a.cuts.cut[i + 1] - a.cuts.cut[i];
-    TNT_TRY(lse_gemm(w.proj, a.d, a.out_w[i], a.d, nullptr, N, ncols, a.d, a.dtype, w.counts + i,
+    TNT_TRY(lse_gemm(fold ? w.xc : w.proj, a.d, fold ? a.fold_w[i] : a.out_w[i], a.d, nullptr, N, ncols, a.d, a.dtype, w.counts + i,
                      w.tail_loc + static_cast<long>(i) * N, nullptr, ncols, nullptr, 0, w.partials,
                      w.tail_stats + static_cast<long>(i) * N, st));
   }
@@ -357,10 +358,11 @@ int adasoftmax_greedy(const AdaSoftmax& a, const void* x, long ldx, int N, int64
   TNT_TRY(lse_gemm(x, ldx, a.head_w, a.d, nullptr, N, a.cuts.cut[0] + nt, a.d, a.dtype, nullptr, nullptr, nullptr,
                    a.cuts.cut[0], w.side, nt, w.partials, w.head_stats, st));
   for (int i = 0; i < nt; ++i) {
-    TNT_TRY(tail_proj(a, i, x, ldx, N, nullptr, w.proj, st));
+    const bool fold = a.use_fold && a.fold_w[i];
+    if (!fold) TNT_TRY(tail_proj(a, i, x, ldx, N, nullptr, w.proj, st));
     const int ncols = a.cuts.cut[i + 1] - a.cuts.cut[i];
-    TNT_TRY(lse_gemm(w.proj, a.d, a.out_w[i], a.d, nullptr, N, ncols, a.d, a.dtype, nullptr, nullptr, nullptr, ncols,
-                     nullptr, 0, w.partials, w.tail_stats + static_cast<long>(i) * N, st));
+    TNT_TRY(lse_gemm(fold ? x : w.proj, fold ? ldx : a.d, fold ? a.fold_w[i] : a.out_w[i], a.d, nullptr, N, ncols, a.d, a.dtype,
+                     nullptr, nullptr, nullptr, ncols, nullptr, 0, w.partials, w.tail_stats + static_cast<long>(i) * N, st));
   }
   greedy_pick_kernel<<<(N + 255) / 256, 256, 0, st>>>(N, a.cuts, w.head_stats, w.side, w.tail_stats, tok, logp);
   TNT_LAUNCHED();
@@ -380,9 +382,11 @@ int adasoftmax_logprob(const AdaSoftmax& a, const void* x, long ldx, int N, floa
   lp.M = N; lp.N = nh; lp.K = a.d; lp.groups = 1; lp.dtype_in = a.dtype; lp.dtype_out = TNT_F32; lp.epilogue = EPI_NONE;
   TNT_TRY(launch_gemm(&lp, -1, nullptr, nullptr, st));
   for (int i = 0; i < nt; ++i) {
-    TNT_TRY(tail_proj(a, i, x, ldx, N, nullptr, w.proj, st));
+    const bool fold = a.use_fold && a.fold_w[i];
+    if (!fold) TNT_TRY(tail_proj(a, i, x, ldx, N, nullptr, w.proj, st));
     tnt_linear_params tp = {};
-    tp.a = w.proj; tp.lda = a.d; tp.w = a.out_w[i]; tp.ldw = a.d; tp.c = out + a.cuts.cut[i]; tp.ldc = V;
+    tp.a = fold ? x : w.proj; tp.lda = fold ? ldx : a.d; tp.w = fold ? a.fold_w[i] : a.out_w[i]; tp.ldw = a.d;
+    tp.c = out + a.cuts.cut[i]; tp.ldc = V;
     tp.M = N; tp.N = a.cuts.cut[i + 1] - a.cuts.cut[i]; tp.K = a.d; tp.groups = 1;
     tp.dtype_in = a.dtype; tp.dtype_out = TNT_F32; tp.epilogue = EPI_NONE;
     TNT_TRY(launch_gemm(&tp, -1, nullptr, nullptr, st));

@@ -15,6 +15,12 @@ struct AdaSoftmax {
   const void* head_w;                       // [cut0 + n_tails, d]  (tied band-0 embedding ; class_proj)
   const void* proj_w[TNT_MAX_CLUSTERS];     // tail i: [d, d]
   const void* out_w[TNT_MAX_CLUSTERS];      // tail i: [cut[i+1]-cut[i], d] (tied band embedding)
+  // inference (static weights, bf16): out_w[i] . proj_w[i] folded once at load time, [cut[i+1]-cut[i], d] -- the tail's
+  // Sequential(Linear(d, d), Dropout(0), Linear(d, n_i)) (fairseq AdaptiveSoftmax tail, softmax.py:42-60) is ONE linear map,
+  // so the per-call projection GEMM of every tail disappears; NULL entries / use_fold == false: the two-GEMM form
+  // (training: the factors are updated every step and their gradients are needed separately)
+  const void* fold_w[TNT_MAX_CLUSTERS];
+  bool use_fold;
 };
 
 size_t lse_partials_bytes(int M, int n_cols);

@@ -70,6 +70,7 @@ size_t plan(tnt_decoder* D, char* base) {
   for (int i = 0; i < nt; ++i) {
     D->ada.proj_w[i] = a.take(d * d * E);
     D->ada.out_w[i] = a.take(static_cast<size_t>(c.cutoffs[i + 1] - c.cutoffs[i]) * d * E);
+    D->ada.fold_w[i] = a.take(static_cast<size_t>(c.cutoffs[i + 1] - c.cutoffs[i]) * d * E);
   }
   D->scratch_dd = a.take(d * d * 4);
   for (int i = 0; i < c.n_clusters; ++i) D->emb_proj[i] = a.take(d * d * E);
@@ -372,6 +373,21 @@ extern "C" int tnt_decoder_finalize(tnt_decoder* D, tnt_stream stream) {
   }
   L.flush();
   if (L.err != TNT_OK) return L.err;
+  // inference, bf16: fold every tail's two linear maps into one (adasoftmax.cuh); a decoder with registered gradient
+  // buffers is being trained -- its factors change every step and are differentiated separately -- and keeps the two GEMMs
+  {
+    static const bool fold_on = [] { const char* e = getenv("TNT_FOLD_TAILS"); return !(e && e[0] == '0'); }();
+    const int nt = c.n_clusters - 1;
+    D->ada.use_fold = fold_on && c.dtype == TNT_BF16 && D->grads.empty() && nt > 0;
+    for (int i = 0; i < nt && D->ada.use_fold; ++i) {
+      tnt_linear_params lp = {};
+      lp.a = D->ada.out_w[i]; lp.lda = d; lp.w = D->ada.proj_w[i]; lp.ldw = d; lp.c = const_cast<void*>(D->ada.fold_w[i]); lp.ldc = d;
+      lp.M = c.cutoffs[i + 1] - c.cutoffs[i]; lp.N = d; lp.K = d; lp.groups = 1; lp.layout = TNT_NN;
+      lp.dtype_in = c.dtype; lp.dtype_out = c.dtype; lp.epilogue = TNT_EPI_NONE;
+      const int rc = tnt_linear_fwd(&lp, stream);
+      if (rc != TNT_OK) return rc;
+    }
+  }
   TNT_CUDA(cudaGetLastError());
   // the raw (fp32 master) pointers are kept: the training backward reads weight_v / weight_g / the band tables
   D->finalized = true;
