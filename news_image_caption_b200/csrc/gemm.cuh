@@ -44,7 +44,9 @@ struct LseExtra {
   const float* row_w = nullptr;
 };
 
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+// (fast reciprocal: the IEEE division compiled to ~20 instructions per gate -- with one epilogue warp per scheduler the GLU
+// GEMM of a layer took as long as the twice larger fc1 GEMM: 21.5 vs 12.2 us for the same shape without the gate)
+__device__ __forceinline__ float sigmoidf_(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
 
 // One thread owns NC consecutive accumulator columns [n0, n0+NC) of row m (n0 % NC == 0).
 // `bias_n0` points at the bias of column n0 (or is null); with `bias_padded` it is a zero-padded staging copy
