@@ -404,6 +404,17 @@ int h2d_source(tnt_decoder* D, void* dst, const void* src_host, const uint8_t* m
     D->zeroed_staging.insert(dst);
   }
   const size_t pitch = static_cast<size_t>(B) * row;
+  {
+    // a source without padding (the image regions: every caption has all S rows) is ONE contiguous copy: every strided
+    // copy costs the DMA engine ~3.5 us of fixed time, 64 of them per step for nothing
+    bool all_live = true;
+    for (int b = 0; b < B && all_live; ++b) all_live = mask_host[static_cast<size_t>(b) * S + S - 1] == 0;
+    if (all_live) {
+      TNT_CUDA(cudaMemcpyAsync(dst, src_host, all, cudaMemcpyHostToDevice, st));
+      if (bytes_out) *bytes_out += all;
+      return TNT_OK;
+    }
+  }
   static const bool zero_copy = [] { const char* e = getenv("TNT_H2D_ZEROCOPY"); return e && e[0] == '1'; }();   // measured slower: off
   const void *src_dev = nullptr, *mask_dev = nullptr;
   if (zero_copy && row % 16 == 0 && aligned16(dst) && aligned16(src_host) && host_dev_ptr(src_host, &src_dev) &&
@@ -580,6 +591,14 @@ extern "C" int64_t tnt_h2d_live_rows(void* dst, const void* src_host, const uint
   if (!mask_host) {
     if (cudaMemcpyAsync(dst, src_host, pitch * S, cudaMemcpyHostToDevice, st) != cudaSuccess) return TNT_ERR_CUDA;
     return static_cast<int64_t>(pitch * S);
+  }
+  {
+    bool all_live = S > 0;
+    for (int b = 0; b < B && all_live; ++b) all_live = mask_host[static_cast<size_t>(b) * S + S - 1] == 0;
+    if (all_live) {                                  // no padding anywhere: one contiguous copy
+      if (cudaMemcpyAsync(dst, src_host, pitch * S, cudaMemcpyHostToDevice, st) != cudaSuccess) return TNT_ERR_CUDA;
+      return static_cast<int64_t>(pitch * S);
+    }
   }
   {
     static const bool zero_copy = [] { const char* e = getenv("TNT_H2D_ZEROCOPY"); return e && e[0] == '1'; }();   // measured slower: off
