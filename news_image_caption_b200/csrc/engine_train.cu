@@ -543,6 +543,9 @@ extern "C" int tnt_decoder_set_grad(tnt_decoder* d, const char* key, float* grad
   return TNT_OK;
 }
 
+static int g_train_side = -1;   // test hook (tnt_debug_train_side_streams): >= 0 overrides TNT_TRAIN_SIDE_STREAMS for decoders
+                                // that have not stepped yet
+
 namespace {
 struct StepSetup {
   TrainWs w;
@@ -568,19 +571,20 @@ int step_setup(tnt_decoder* D, const tnt_contexts* ctx, void* workspace, size_t 
     const char* n = getenv("TNT_TRAIN_SIDE_STREAMS");
     return n ? std::max(0, std::min(atoi(n), static_cast<int>(tnt_decoder::kSideStreams))) : 3;
   }();
-  if (want_side && !D->side_fork) {
+  const int want = g_train_side >= 0 ? std::min(g_train_side, static_cast<int>(tnt_decoder::kSideStreams)) : want_side;
+  if (want && !D->side_fork) {
     int lo = 0, hi = 0;
     TNT_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     // measured (B = 64, one GPU): with ONE side stream the highest priority was better (7.05 vs 7.12 ms per step), with three
     // the lowest is (6.57 vs 6.62 ms): the chain is the critical path, freed SMs go to its next kernel first
     const char* pe = getenv("TNT_SIDE_PRIO");
-    for (int k = 0; k < want_side; ++k) {
+    for (int k = 0; k < want; ++k)
       TNT_CUDA(cudaStreamCreateWithPriority(&D->side_streams[k], cudaStreamNonBlocking, (pe && pe[0] == 'h') ? hi : lo));
-      TNT_CUDA(cudaEventCreateWithFlags(&D->side_join[k], cudaEventDisableTiming));
-    }
+    // (all kSideStreams join events: the loss backward also uses them as per-tail "chain done" events, whatever `want`)
+    for (int k = 0; k < tnt_decoder::kSideStreams; ++k) TNT_CUDA(cudaEventCreateWithFlags(&D->side_join[k], cudaEventDisableTiming));
     TNT_CUDA(cudaStreamCreateWithFlags(&D->stage_stream, cudaStreamNonBlocking));
     TNT_CUDA(cudaEventCreateWithFlags(&D->side_fork, cudaEventDisableTiming));
-    D->n_side = want_side;
+    D->n_side = want;
   }
   while (static_cast<int>(D->stage_events.size()) < Ls + 2) {
     cudaEvent_t e;
@@ -793,6 +797,8 @@ extern "C" int tnt_decoder_train_backward(tnt_decoder* D, const int64_t* ids, co
   D->pending_ws = nullptr;
   return train_backward(D, ids, target, ctx, loss_scale, out2, s.w, D->pending_dr_on ? &D->pending_drc : nullptr, as_stream(stream));
 }
+
+extern "C" void tnt_debug_train_side_streams(int n) { g_train_side = n; }
 
 extern "C" int tnt_decoder_train_stages(const tnt_decoder* d) { return d ? d->cfg.n_layers + 2 : 0; }
 

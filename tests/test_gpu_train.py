@@ -340,6 +340,53 @@ def test_trainer_two_steps_match_oracle_bert_adam():
     assert worst[0] < 1e-3, worst
 
 
+@pytest.mark.parametrize('dtype,tol', [(torch.float32, 1e-5), (torch.bfloat16, 2e-3)])
+def test_parameter_gradient_streams_do_not_change_the_gradients(dtype, tol):
+    """The training backward issues every parameter gradient on side streams beside the data-gradient chain
+    (engine_train.cu); with all of it on the caller's stream (0 side streams) the step must give the same loss and gradients."""
+    from news_image_caption_b200 import _lib
+    f = torch.load(os.path.join(G, 'tell2_small.pt'), weights_only=False)
+    cfg = f['config']
+    ctx = {k: v.cuda() for k, v in f['contexts'].items()}
+    L = _lib.lib()
+    res = {}
+    try:
+        for n in (0, 3, 1):
+            L.tnt_debug_train_side_streams(n)
+            dec = make_decoder(cfg, f['state_dict'], dtype).enable_training()
+            for _ in range(2):                      # the second step reuses the per-parity buffers of the first
+                out = dec.train_step(f['prev'].cuda(), f['target'].cuda(), ctx).clone()
+            torch.cuda.synchronize()
+            res[n] = (out, dec.flat_grads.clone())
+    finally:
+        L.tnt_debug_train_side_streams(-1)
+    for n in (3, 1):
+        assert rel_err(res[n][0], res[0][0]) < tol
+        assert rel_err(res[n][1], res[0][1]) < tol
+
+
+def test_stage_wise_bert_adam_equals_the_single_pass(monkeypatch):
+    """Trainer with TNT_STAGE_ADAM=1 (per-tensor clipping makes a stage's slice of the arena steppable as soon as its
+    gradients are final: norms + BertAdam slice by slice behind the stage events, the band tables last) must end with the
+    same parameters and moments as the single pass over the whole arena after the backward."""
+    from news_image_caption_b200.trainer import Trainer
+    f = torch.load(os.path.join(G, 'tell2_small.pt'), weights_only=False)
+    cfg = f['config']
+    ctx = {k: v.cuda() for k, v in f['contexts'].items()}
+    res = {}
+    for mode in ('0', '1'):
+        monkeypatch.setenv('TNT_STAGE_ADAM', mode)
+        dec = make_decoder(cfg, f['state_dict'], torch.float32)
+        tr = Trainer(dec, lr=1e-2, max_grad_norm=0.1, weight_decay=1e-3, t_total=10, warmup=0.2)
+        assert tr.stage_adam == (mode == '1')
+        for _ in range(3):
+            out = tr.step(f['prev'].cuda(), f['target'].cuda(), ctx)
+        torch.cuda.synchronize()
+        res[mode] = (dec.flat_params.clone(), tr.m.clone(), tr.v.clone(), out.clone())
+    for a, b in zip(res['0'], res['1']):
+        assert rel_err(a, b) < 1e-6
+
+
 def test_train_step_full_width_bf16():
     """BASELINE.json model width (d=1024, 16 heads of 64, ffn 4096, V=50265, cutoffs 5000/20000), 2 layers:
     the tcgen05 paths (NT / NN / TN GEMMs, attention forward + backward, softmax-gradient epilogue) against
