@@ -235,7 +235,7 @@ def timed(env, step, steps, warmup, prof_names):
     ms = torch.tensor([e0.elapsed_time(e1)], device='cuda')
     if env.world > 1:
         env.dist.all_reduce(ms, op=env.dist.ReduceOp.MAX)
-    return dict(ms_total=ms.item(), launches=int(launches), clocks=clocks, prof=prof, out=out)
+    return dict(ms_total=ms.item(), launches=int(launches), clocks=clocks, prof=prof, out=out, steps=steps)
 
 
 def all_sum(env, x):
@@ -261,22 +261,36 @@ def peak_for(clocks, tf_burst, tf_sus, which):
            (tf_sus, which + ' bf16_tflops_sustained (SM clock %s of %s MHz during the timed loop)' % (mhz, mx))
 
 
-def kv_roofline(B, t, ms_per_step):
-    """Dominant kernel of the teacher-forced / training step: the tcgen05 GEMM that projects K/V of the article for all
-    layers, M = S_art * B rows, N = L * 2d, K = 1024; timed by CUDA events inside the timed loop (tnt_prof_*)."""
+def kv_roofline(B, t, ms_per_step, L=None):
+    """Dominant kernel of the teacher-forced / training step: the tcgen05 GEMM that projects K/V of the article, M = S_art * B
+    rows, K = 1024; timed by CUDA events inside the timed loop (tnt_prof_*, on the stream the GEMM is launched on).  The
+    default is ONE launch for all layers (N = L * 2d).  With TNT_KV_BESIDE_SMS / TNT_KV_INLINE set (measured slower, off by
+    default: DESIGN.md section 4) the forward issues it once per LAYER (N = 2d); under TNT_KV_BESIDE_SMS on a side stream whose
+    grids are sized for a share of the SMs, beside the layer chain: then `achieved` is what one such launch reaches while it
+    shares the GPU, `sm_share` the fraction of the SMs its grid covers and `frac_of_share` = achieved / (peak * sm_share)."""
     hbm, tf_burst, tf_sus, which = peaks()
     kv_ms, kv_n = t['prof']['kv_proj.article']
-    M, N, K = S_ART * B, 4 * 2 * 1024, 1024
+    per_step = max(1, round(kv_n / max(t.get('steps', kv_n), 1)))
+    M, N, K = S_ART * B, 4 * 2 * 1024 // per_step, 1024
     gemm_ms = kv_ms / max(kv_n, 1)
     flops = 2.0 * M * N * K
     achieved = flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     peak, src = peak_for(t['clocks'], tf_burst, tf_sus, which)
-    return {'bound': 'tensor', 'kernel': 'gemm_tc_kernel<EPI_NONE,bf16,CG=2> (article K/V projection, all layers)',
-            'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s', 'frac': achieved / peak,
-            'traffic': TRAFFIC_KV_GEMM * B / 64.0 if B == 64 else None, 'peak_source': src,
-            'frac_of_burst_peak': achieved / tf_burst, 'frac_of_sustained_peak': achieved / tf_sus,
-            'flops_per_launch': flops, 'shape': [M, N, K], 'ms_per_launch': gemm_ms, 'launches_timed': kv_n,
-            'share_of_step': gemm_ms / ms_per_step if ms_per_step else None}
+    r = {'bound': 'tensor', 'kernel': 'gemm_tc_kernel<EPI_NONE,bf16,CG=2> (article K/V projection, %s)' %
+         ('all layers in one launch' if per_step == 1 else 'one layer per launch, %d launches per step beside the layer chain' % per_step),
+         'achieved': achieved, 'peak': peak, 'unit': 'TFLOP/s', 'frac': achieved / peak,
+         'traffic': TRAFFIC_KV_GEMM * B / 64.0 / per_step if B == 64 else None, 'peak_source': src,
+         'frac_of_burst_peak': achieved / tf_burst, 'frac_of_sustained_peak': achieved / tf_sus,
+         'flops_per_launch': flops, 'shape': [M, N, K], 'ms_per_launch': gemm_ms, 'launches_timed': kv_n,
+         'share_of_step': per_step * gemm_ms / ms_per_step if ms_per_step else None}
+    if per_step > 1 and L is not None and int(L.tnt_debug_kv_beside_get()) > 0:
+        sms = int(L.tnt_debug_kv_beside_get())
+        n_sm = torch.cuda.get_device_properties(0).multi_processor_count
+        r['sm_share'] = sms / n_sm
+        r['sms'] = [sms, n_sm]
+        r['frac_of_share'] = achieved / (peak * sms / n_sm)
+        r['note'] = 'the launch shares the GPU with the layer chain: share_of_step counts its duration, not its exclusive time'
+    return r
 
 
 def sample_rows(ctx, tgt, n):
@@ -489,7 +503,7 @@ def bench_forward(env, wl, dec, sd, args, with_sustained=False):
                   'captions_per_sec': B * env.world * args.steps / e2e_s, 'ms_per_step': 1e3 * e2e_s / args.steps,
                   'repetitions_ms_per_step': [round(1e3 * r / args.steps, 4) for r in reps], 'reported': 'median of 5 repetitions of K steps'}
     if env.rank == 0:
-        res['roofline'] = kv_roofline(B, t, ms_step)
+        res['roofline'] = kv_roofline(B, t, ms_step, env.L)
         if not args.no_parity:
             res['parity'] = parity_forward(dec, sd, w['sources'], prev, tgt, ctx, keep['X'], keep['attn'])
     if with_sustained:
@@ -520,11 +534,13 @@ def bench_forward(env, wl, dec, sd, args, with_sustained=False):
         ms_s = e0.elapsed_time(e1) / chunk
         hbm, tf_burst, tf_sus, which = peaks()
         g_ms = kv[0] / max(kv[1], 1)
-        ach = 2.0 * S_ART * B * 8192 * 1024 / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
+        per_step = max(1, round(kv[1] / chunk))                     # 4: one projection launch per layer (project_kv_beside)
+        ach = 2.0 * S_ART * B * (8192 // per_step) * 1024 / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
         res['sustained'] = {'ms_per_step': ms_s, 'tokens_per_sec_per_gpu': ntok / (ms_s * 1e-3), 'steps_before': n_done,
                             'steps_timed': chunk, 'seconds': time.perf_counter() - t_start, 'sm_mhz_median': clocks['sm_mhz'],
                             'sm_max_mhz': clocks['sm_max_mhz'], 'reasons': clocks['reasons'],
-                            'kv_gemm_tflops': ach, 'kv_gemm_frac_of_sustained_peak': ach / tf_sus, 'kv_gemm_ms': g_ms}
+                            'kv_gemm_tflops': ach, 'kv_gemm_frac_of_sustained_peak': ach / tf_sus, 'kv_gemm_ms': g_ms,
+                            'kv_gemm_launches_per_step': per_step}
     return res
 
 

@@ -234,6 +234,9 @@ _SIGS = {
     'tnt_debug_gemm_single_acc': (None, [i32]),
     'tnt_debug_gemm_split_k': (None, [i32]),
     'tnt_debug_sub_batches': (None, [i32]),
+    'tnt_debug_kv_beside': (None, [i32]),
+    'tnt_debug_kv_inline': (None, [i32]),
+    'tnt_debug_kv_beside_get': (i32, []),
     'tnt_debug_train_side_streams': (None, [i32]),
     'tnt_debug_force_simt_attention': (None, [i32]),
     'tnt_debug_force_simt_attention_bwd': (None, [i32]),

@@ -19,7 +19,7 @@ enum Variant {
   V_XATTN_TC, V_XATTN_TC_TILESKIP, V_XATTN_TC_WEIGHTS, V_XATTN_SIMT, V_XATTN_STEP, V_XATTN_SHORT,
   V_XATTN_BWD_TC, V_XATTN_BWD_SIMT,
   V_DYNCONV_FWD_TC, V_DYNCONV_FWD_SIMT, V_DYNCONV_BWD_TC, V_DYNCONV_BWD_SIMT, V_DYNCONV_STEP_FAST, V_DYNCONV_STEP_SIMT,
-  V_LN_GEMM_FUSED, V_COUNT
+  V_LN_GEMM_FUSED, V_KV_BESIDE, V_COUNT
 };
 void variant_hit(Variant v);
 bool prof_enabled();

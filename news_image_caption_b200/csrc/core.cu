@@ -35,7 +35,7 @@ static const char* const kVariantNames[V_COUNT] = {
     "xattn.tc", "xattn.tc.tileskip", "xattn.tc.weights", "xattn.simt", "xattn.step", "xattn.short",
     "xattn_bwd.tc", "xattn_bwd.simt",
     "dynconv.fwd.tc", "dynconv.fwd.simt", "dynconv.bwd.tc", "dynconv.bwd.simt", "dynconv.step.fast", "dynconv.step.simt",
-    "gemm.ln_fused"};
+    "gemm.ln_fused", "kv.beside"};
 void variant_hit(Variant v) { g_variants[v].fetch_add(1, std::memory_order_relaxed); }
 void count_launch(int n) { g_launches.fetch_add(static_cast<uint64_t>(n), std::memory_order_relaxed); }
 

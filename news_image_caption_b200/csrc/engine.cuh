@@ -73,6 +73,11 @@ struct tnt_decoder {
   static constexpr int kMaxSub = 4;
   cudaStream_t sub_streams[kMaxSub - 1] = {};
   cudaEvent_t sub_fork = nullptr, sub_join[kMaxSub - 1] = {};
+  // teacher-forced forward: the memory K/V projections run layer by layer on this stream, on a share of the SMs, beside the
+  // latency-bound layer chain (engine_fwd.cu: project_kv_beside); kv_ready[l] = layer l's K/V of every source are written
+  cudaStream_t kv_stream = nullptr;
+  cudaEvent_t kv_fork = nullptr;
+  std::vector<cudaEvent_t> kv_ready;
   std::map<std::string, float*> grads; // training: fp32 gradient buffer per state_dict key (tnt_decoder_set_grad)
   // data-parallel training: embedding-row gradients go to a packed list instead of the dense band tables
   void* sparse_rows = nullptr; long long* sparse_meta = nullptr; int* sparse_count = nullptr; int sparse_capacity = 0;
@@ -115,6 +120,7 @@ struct FwdWs {
   float* step_scores = nullptr;  // generation through the copy head: [B, H, S_w + 2] score dump of the decode-step attention
   float* step_lse = nullptr;     //   and its [B, H] log-sum-exp
   int kv_B = 0;                  // context entries the K/V buffers hold when the rows are a SUB-batch of them (0: B / kv_group)
+  const cudaEvent_t* kv_ready = nullptr;   // [n_layers] or NULL: run_layer makes its stream wait for kv_ready[l] before layer l's attention
   size_t total;
 };
 // Sub-batches.  At the benchmark's batch sizes every kernel of a decoder layer is latency-bound (a 2048-row GEMM is one wave

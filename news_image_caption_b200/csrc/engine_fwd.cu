@@ -200,6 +200,121 @@ int project_kv(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStre
   return TNT_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// K/V projections BESIDE the layer chain (teacher-forced forward) -- MEASURED SLOWER, off unless TNT_KV_BESIDE_SMS / the test
+// hook asks for it.  The idea: the projections are throughput-bound (article: 550 GF at B = 64, 0.39 ms on the whole GPU) and
+// nothing in a layer needs them before its attention, while the layer chain is latency-bound (14 dependent launches of
+// 6-22 us per layer for ~55 us of tensor work).  So the projections run layer by layer (W rows / output columns
+// [l*2d, (l+1)*2d) of the fused per-source projection: the same dot products as the one-GEMM form) on a library-owned stream
+// with their persistent grids sized for `sms` SMs, the chain keeps the other SMs, and layer l's attention waits for
+// kv_ready[l].  Sources with few rows keep the one-GEMM form up front.  Result (B200, tools/sweep_kv_beside.py,
+// profiles/r2_kv_beside_sweep.txt): C2 1.41 ms in the plain order, 1.47-1.66 ms at every share from 56 to 132 SMs: the chain's
+// one-wave GEMMs (128 tiles) take 2-3 CTA waves on the SMs the projections leave them and stretch 12 -> 30-55 us each.
+constexpr int kKvBesideSms = 104; // share of the projections when the mode is asked for without a number (best of the sweep)
+static int g_kv_beside = -1;      // test hook (tnt_debug_kv_beside): -1 automatic, 0 off, > 0 on with that many SMs
+
+int kv_beside_sms(const tnt_decoder* D, const tnt_contexts* ctx) {
+  static const int env = [] { const char* e = getenv("TNT_KV_BESIDE_SMS"); return e ? atoi(e) : -1; }();
+  const int want = g_kv_beside >= 0 ? g_kv_beside : env;
+  if (want == 0 || sm_budget() > 0) return 0;          // (a caller that already shares the SMs keeps the plain order)
+  long rows = 0;
+  for (int s = 0; s < D->cfg.n_sources; ++s) rows += static_cast<long>(ctx->S[s]) * ctx->B;
+  if (want < 0 || rows == 0) return 0;      // measured slower than the plain order at every share: off unless asked for
+  const int all = num_sms();
+  const int sms = want > 0 ? want : kKvBesideSms;
+  return std::max(2, std::min(sms, all)) & ~1;
+}
+
+// which sources are projected layer by layer (the others keep the one-GEMM form, issued by kv_prologue)
+struct KvByLayer { bool on[TNT_MAX_SOURCES] = {}; };
+
+// extra rows + live-tile words of every source, and the one-GEMM projection of the sources that are NOT split by layer
+int kv_prologue(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, cudaStream_t ks, long min_rows, KvByLayer* bl) {
+  const tnt_decoder_config& c = D->cfg;
+  const int ldkv = c.n_layers * 2 * c.d;
+  if (w.sched) TNT_CUDA(cudaMemsetAsync(w.sched, 0, 2 * tnt_decoder::kMaxSub * sizeof(int), ks));
+  for (int s = 0; s < c.n_sources; ++s) {
+    const int grid = std::min<long>((static_cast<long>(ctx->B) * ldkv + 255) / 256, 4L * num_sms());
+    const bool scan = w.tile_live[s] && ctx->pad_mask[s] && ctx->S[s] > 0;
+    const int extra = scan ? (ctx->B + 7) / 8 : 0;
+    if (c.dtype == TNT_BF16)
+      kv_extra_rows_kernel<bf16><<<grid + extra, 256, 0, ks>>>(static_cast<bf16*>(w.kv[s]), D->kvrow[s], ctx->S[s], ctx->B, ldkv,
+                                                               grid, ctx->pad_mask[s], w.tile_live[s]);
+    else
+      kv_extra_rows_kernel<float><<<grid + extra, 256, 0, ks>>>(static_cast<float*>(w.kv[s]), D->kvrow[s], ctx->S[s], ctx->B, ldkv,
+                                                                grid, ctx->pad_mask[s], w.tile_live[s]);
+    TNT_LAUNCHED();
+    if (ctx->S[s] == 0) continue;
+    TNT_CHECK_ARG(ctx->memory[s], "decoder: context '%s' missing", c.source_names[s]);
+    bl->on[s] = static_cast<long>(ctx->S[s]) * ctx->B >= min_rows;
+    if (bl->on[s]) continue;
+    TNT_TRY(linear(ctx->memory[s], c.source_dim[s], D->wkv[s], c.source_dim[s], D->bkv[s], w.kv[s], ldkv,
+                   ctx->S[s] * ctx->B, ldkv, c.source_dim[s], c.dtype, EPI_NONE, nullptr, 0, ks));
+  }
+  return TNT_OK;
+}
+
+// layer l's K/V of the split sources: W rows / output columns [l*2d, (l+1)*2d) of the fused projection
+int kv_layer(tnt_decoder* D, const tnt_contexts* ctx, const FwdWs& w, int l, cudaStream_t ks, const KvByLayer& bl) {
+  const tnt_decoder_config& c = D->cfg;
+  const int ldkv = c.n_layers * 2 * c.d;
+  const size_t E = D->esz(), n0 = static_cast<size_t>(l) * 2 * c.d;
+  for (int s = 0; s < c.n_sources; ++s) {
+    if (!bl.on[s]) continue;
+    int pid = -1;
+    if (prof_enabled()) {
+      char pname[40];
+      snprintf(pname, sizeof(pname), "kv_proj.%s", c.source_names[s]);
+      pid = prof_begin(pname, ks);
+    }
+    TNT_TRY(linear(ctx->memory[s], c.source_dim[s], static_cast<const char*>(D->wkv[s]) + n0 * c.source_dim[s] * E, c.source_dim[s],
+                   D->bkv[s] ? D->bkv[s] + n0 : nullptr, static_cast<char*>(w.kv[s]) + n0 * E, ldkv, ctx->S[s] * ctx->B, 2 * c.d,
+                   c.source_dim[s], c.dtype, EPI_NONE, nullptr, 0, ks));
+    prof_end(pid, ks);
+  }
+  return TNT_OK;
+}
+
+int project_kv_beside(tnt_decoder* D, const tnt_contexts* ctx, FwdWs& w, cudaStream_t st, int sms) {
+  const tnt_decoder_config& c = D->cfg;
+  if (!D->kv_stream) {
+    TNT_CUDA(cudaStreamCreateWithFlags(&D->kv_stream, cudaStreamNonBlocking));
+    TNT_CUDA(cudaEventCreateWithFlags(&D->kv_fork, cudaEventDisableTiming));
+  }
+  while (static_cast<int>(D->kv_ready.size()) < c.n_layers) {
+    cudaEvent_t e;
+    TNT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    D->kv_ready.push_back(e);
+  }
+  cudaStream_t ks = D->kv_stream;
+  // the side stream sees everything issued on `st` so far: the contexts' uploads, and the previous call's attention reads of
+  // the K/V buffers this call overwrites
+  TNT_CUDA(cudaEventRecord(D->kv_fork, st));
+  TNT_CUDA(cudaStreamWaitEvent(ks, D->kv_fork, 0));
+  SmBudget budget(sms);
+  KvByLayer bl;
+  TNT_TRY(kv_prologue(D, ctx, w, ks, 2048, &bl));
+  for (int l = 0; l < c.n_layers; ++l) {
+    TNT_TRY(kv_layer(D, ctx, w, l, ks, bl));
+    TNT_CUDA(cudaEventRecord(D->kv_ready[l], ks));
+  }
+  w.kv_ready = D->kv_ready.data();
+  variant_hit(V_KV_BESIDE);
+  return TNT_OK;
+}
+
+// K/V projections of the large sources INLINE, layer by layer: layer l's slice is issued on the step's own stream right before
+// layer l, so that its attention finds the (live part of the) 135 MB it reads in the 126 MB L2 instead of in HBM.  MEASURED: the
+// article attention stays at 30 us per layer (it is not HBM-bound at this size) and the four narrower GEMMs cost 4 x 100 us
+// instead of 388 us: C2 1.40 -> 1.42 ms, C4 2.96 -> 3.07 ms (tools/ab_kv_inline.py).  Off unless TNT_KV_INLINE=1 / the test hook.
+static int g_kv_inline = -1;      // test hook (tnt_debug_kv_inline): -1 automatic, 0 off, 1 on
+bool kv_inline_on(const tnt_decoder* D, const tnt_contexts* ctx) {
+  static const int env = [] { const char* e = getenv("TNT_KV_INLINE"); return e ? atoi(e) : -1; }();
+  const int want = g_kv_inline >= 0 ? g_kv_inline : env;
+  (void)D; (void)ctx;
+  return want > 0;
+}
+
 int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, const void* Xin, void* Xout, int B, int T,
               void* ring, const int* pos, float* attn_out, bool transpose_out, cudaStream_t st, int kv_group,
               const tnt_dropout_config* dr, const ConvHist* ch) {
@@ -260,6 +375,7 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
   // multi-source cross attention: one stacked query projection, per-source attention, grouped out-proj
   TNT_TRY(linear(w.X1, d, L.wq, d, L.bq, w.Q, static_cast<long>(ns) * d, N, ns * d, d, dt, EPI_NONE, nullptr, 0, st, 1, 0, 0, 0, 0, 0,
                  L.wo, ns * dd));
+  if (w.kv_ready) TNT_CUDA(cudaStreamWaitEvent(st, w.kv_ready[l], 0));   // K/V of this layer come from the side stream (project_kv_beside)
   const long ldkv = static_cast<long>(c.n_layers) * 2 * d;
   tnt_xattn_params aps[TNT_MAX_SOURCES];
   bool all_step = T == 1;
@@ -358,6 +474,15 @@ int embed(tnt_decoder* D, const int64_t* ids, int B, int T, void* out, const int
 using namespace tnt;
 
 extern "C" void tnt_debug_sub_batches(int n) { tnt::g_sub_batches = n > 0 ? n : 0; }
+extern "C" void tnt_debug_kv_beside(int sms) { tnt::g_kv_beside = sms; }
+extern "C" void tnt_debug_kv_inline(int on) { tnt::g_kv_inline = on; }
+// SMs the K/V projections' grids are sized for when the forward runs them beside the layer chain (0: that mode is off)
+extern "C" int tnt_debug_kv_beside_get(void) {
+  const char* e = getenv("TNT_KV_BESIDE_SMS");
+  const int want = tnt::g_kv_beside >= 0 ? tnt::g_kv_beside : e ? atoi(e) : -1;
+  if (want == 0) return 0;
+  return std::max(2, std::min(want > 0 ? want : tnt::kKvBesideSms, tnt::num_sms())) & ~1;
+}
 
 extern "C" size_t tnt_decoder_workspace_bytes(const tnt_decoder* d, int B, int T, const int* S) {
   if (!d || !S) return 0;
@@ -378,10 +503,15 @@ extern "C" int tnt_decoder_forward(tnt_decoder* D, const int64_t* ids, const tnt
     return TNT_ERR_WORKSPACE;
   }
   cudaStream_t st = as_stream(stream);
-  TNT_TRY(project_kv(D, ctx, w, st));
   // sub-batches (engine.cuh): the layer chains of a few row ranges side by side, each on its own stream
   SubBatches sb;
   TNT_TRY(sub_plan(D, B, 1, 16, st, &sb));
+  const int kv_sms = sb.n > 1 ? 0 : kv_beside_sms(D, ctx);
+  const bool kv_inline = !kv_sms && sb.n == 1 && kv_inline_on(D, ctx);
+  KvByLayer kv_bl;
+  if (kv_sms) TNT_TRY(project_kv_beside(D, ctx, w, st, kv_sms));
+  else if (kv_inline) TNT_TRY(kv_prologue(D, ctx, w, st, 16384, &kv_bl));
+  else TNT_TRY(project_kv(D, ctx, w, st));
   const int Ls = D->cfg.n_layers;
   const size_t E = D->esz();
   TNT_TRY(sub_fork(D, sb));
@@ -401,6 +531,7 @@ extern "C" int tnt_decoder_forward(tnt_decoder* D, const int64_t* ids, const tnt
       float* ao = nullptr;
       if (last && attn_out && D->article_idx >= 0)
         ao = attn_out + static_cast<size_t>(b0) * T * (ctx->S[D->article_idx] + 2);
+      if (kv_inline) TNT_TRY(kv_layer(D, ctx, w, l, st, kv_bl));
       TNT_TRY(run_layer(D, l, &ci, wi, cur, out, nb, T, nullptr, nullptr, ao, last, sb.st[i]));
       cur = out;
     }

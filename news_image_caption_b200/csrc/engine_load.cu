@@ -219,6 +219,9 @@ extern "C" void tnt_decoder_destroy(tnt_decoder* d) {
   for (cudaStream_t& s : d->sub_streams) st(s);
   for (cudaEvent_t& e : d->sub_join) ev(e);
   ev(d->sub_fork);
+  st(d->kv_stream);
+  ev(d->kv_fork);
+  for (cudaEvent_t& e : d->kv_ready) ev(e);
   st(d->copy_stream);
   for (cudaStream_t& s : d->copy_extra) st(s);
   for (cudaEvent_t& e : d->ev_cx_join) ev(e);

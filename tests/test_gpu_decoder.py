@@ -437,6 +437,56 @@ def test_incremental_state_protocol_details():
         assert rel_err(Xa, Xb[sel]) < tol
 
 
+@pytest.mark.parametrize('sources', [('image', 'article'), ('image', 'article', 'faces', 'obj')])
+@pytest.mark.parametrize('mode', ['beside48', 'beside148', 'inline'])
+def test_kv_projections_layer_by_layer_equal_the_plain_order(sources, mode):
+    """Two other schedules of the memory K/V projections in the teacher-forced forward, both measured slower than the plain
+    order and off by default, both kept behind TNT_KV_BESIDE_SMS / TNT_KV_INLINE and these hooks:
+    `beside` = layer by layer on the library's side stream, grids sized for a share of the SMs, while the layer chain runs
+    (layer l's attention waits for an event); `inline` = layer l's slice of the large sources on the step's own stream right
+    before layer l.  Same dot products either way; the tolerance only covers a different split-K plan of the narrower
+    per-layer GEMMs.  Three calls in a row: the second and third overwrite K/V buffers the previous call's attention has just
+    read (the side stream must wait for it), and the loss that follows on the caller's stream must see the joined result."""
+    from news_image_caption_b200 import _lib
+    from news_image_caption_b200.decoder import random_state_dict
+    cfg = dict(d=1024, heads=16, ffn=4096, kernels=[3, 7, 15, 31], vocab=50265, cutoffs=[5000, 20000, 50265],
+               sources=list(sources))
+    sd = random_state_dict(seed=0, sources=sources)
+    L = _lib.lib()
+    B = 40 if mode == 'inline' else 7            # inline splits sources from 16384 rows (article: 512 * 40), beside from 2048
+    batches = [synth.make_batch(B, 32, 50265, sources, seed=s) for s in (123, 124, 125)]
+    sms = int(mode[6:]) if mode.startswith('beside') else 0
+    for dtype, tol in ((torch.float32, 1e-5), (torch.bfloat16, 1e-2)):
+        dec = make_decoder(cfg, sd, dtype)
+        L.tnt_debug_kv_beside(0)
+        L.tnt_debug_kv_inline(0)
+        try:
+            plain = []
+            for prev, tgt, ctx in batches:
+                X, ex = dec(prev.cuda(), cuda_ctx(ctx))
+                plain.append((X.clone(), ex['attn'].clone(), dec.nll(X, tgt.cuda()).clone()))
+            n0 = L.tnt_variant_count(b'kv.beside')
+            if sms:
+                L.tnt_debug_kv_beside(sms)
+                assert L.tnt_debug_kv_beside_get() == min(sms, torch.cuda.get_device_properties(0).multi_processor_count) & ~1
+            else:
+                L.tnt_debug_kv_inline(1)
+            other = []
+            for prev, tgt, ctx in batches:                      # back to back, no synchronisation in between
+                X, ex = dec(prev.cuda(), cuda_ctx(ctx))
+                other.append((X, ex['attn'], dec.nll(X, tgt.cuda())))
+            torch.cuda.synchronize()
+            assert L.tnt_variant_count(b'kv.beside') == n0 + (len(batches) if sms else 0)
+        finally:
+            L.tnt_debug_kv_beside(-1)
+            L.tnt_debug_kv_inline(-1)
+        for (X1, a1, l1), (X2, a2, l2) in zip(plain, other):
+            assert rel_err(X2, X1) < tol
+            assert rel_err(a2, a1) < tol
+            assert int(l1[1].item()) == int(l2[1].item())
+            assert abs(l2[0].item() - l1[0].item()) < tol * abs(l1[0].item())
+
+
 @pytest.mark.parametrize('n_sub', [2, 3])
 def test_sub_batched_forward_and_generation_equal_the_single_chain(full_model, n_sub):
     """The engine can cut a batch into sub-batches whose layer chains run on their own streams (engine.cuh SubBatches;

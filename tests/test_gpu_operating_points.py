@@ -33,7 +33,7 @@ def variants():
     L = _lib.lib()
     names = ['gemm.tc.1cta', 'gemm.tc.pair', 'gemm.splitk', 'gemm.simt', 'xattn.tc', 'xattn.tc.tileskip', 'xattn.tc.weights',
              'xattn.simt', 'xattn.step', 'xattn.short', 'xattn_bwd.tc', 'xattn_bwd.simt', 'dynconv.fwd.tc', 'dynconv.fwd.simt',
-             'dynconv.bwd.tc', 'dynconv.bwd.simt', 'dynconv.step.fast', 'dynconv.step.simt']
+             'dynconv.bwd.tc', 'dynconv.bwd.simt', 'dynconv.step.fast', 'dynconv.step.simt', 'kv.beside']
     return {n: L.tnt_variant_count(n.encode()) for n in names}
 
 
@@ -120,6 +120,7 @@ def _forward_case(models, tag, B, need_attn):
 def test_c2_forward_B64_sampled_rows(models, need_attn):
     """BASELINE configs[1]: 2-source bf16 forward + AdaptiveLoss at B=64 -- the bench's headline step."""
     v = _forward_case(models, '2src', 64, need_attn)
+    assert v['kv.beside'] == 0               # the plain order (side-stream K/V projections measured slower: off by default)
     assert v['gemm.tc.pair'] >= 2            # the image and article K/V projections take the cta_group::2 kernel at this size
     assert v['gemm.simt'] == 0 and v['xattn.simt'] == 0, v      # no fp32 SIMT fallback anywhere in the default bf16 path
     # 4 layers: the article on the tcgen05 kernel (key-padding mask: live-tile lists on), the image regions (51 keys) on the
@@ -132,6 +133,7 @@ def test_c2_forward_B64_sampled_rows(models, need_attn):
 def test_c4_forward_B128_four_sources_sampled_rows(models):
     """BASELINE configs[3]: NYTimes800k 4-source (image + article + faces + objects) bf16 forward at B=128."""
     v = _forward_case(models, '4src', 128, True)
+    assert v['kv.beside'] == 0
     assert v['gemm.tc.pair'] >= 3
     assert v['gemm.simt'] == 0 and v['xattn.simt'] == 0, v
     assert v['xattn.tc'] == 4 and v['xattn.tc.weights'] == 1     # the article; image + faces + objects share ONE short-source
