@@ -193,6 +193,21 @@ typedef struct {
 } tnt_layernorm_params;
 int tnt_layernorm_fwd(const tnt_layernorm_params* p, tnt_stream stream);
 
+/* Linear + residual + LayerNorm in ONE launch: c = LayerNorm(a . w^T + bias + residual) * gamma + beta (bf16 in / out, fp32
+ * statistics, biased variance, eps inside the sqrt).  Replaces the three GEMM -> add -> nn.LayerNorm sites of a decoder layer
+ *   linear2 -> +residual -> conv_layer_norm              ttl/tell/models/decoder_flattened.py:283-291
+ *   out_proj[source] -> +residual -> context_attn_lns[source]   decoder_flattened.py:300-330, decoder_faces_objects.py:310-378
+ *   fc2 -> +residual -> final_layer_norm                 decoder_flattened.py:336-345
+ * `lin` is read as for tnt_linear_fwd with epilogue TNT_EPI_RESIDUAL (or TNT_EPI_NONE: no residual); lin->c receives the
+ * NORMALISED rows.  Grouped problems normalise the N columns of every group on their own with gamma / beta block
+ * g * stride_gb.  transpose_T/_B > 0 (one group, T * B == M): output row t*B + b is written to row b*T + t.
+ * Supported (tnt_linear_ln_supported): TNT_NT, bf16, N = C * BN with C <= 8 CTAs per cluster and BN in {64, 128, 256}
+ * (N = 512 ... 2048), no m_dyn, no dropout, 16-byte aligned operands.  A cluster of C CTAs owns a 128-row block; the row
+ * statistics cross it through distributed shared memory (csrc/gemm_ln.cu). */
+int tnt_linear_ln_supported(const tnt_linear_params* lin, const float* gamma, const float* beta);
+int tnt_linear_ln_fwd(const tnt_linear_params* lin, const float* gamma, const float* beta, int64_t stride_gb, float eps,
+                      int transpose_T, int transpose_B, tnt_stream stream);
+
 typedef struct {
   const void* x; int64_t ldx;     /* forward input */
   const void* dy; int64_t lddy;
@@ -630,13 +645,17 @@ int tnt_decoder_score_host(tnt_decoder* d, const int64_t* ids_host, const int64_
                            tnt_stream stream);
 
 /* Only the LIVE rows of a masked memory source cross PCIe: for caption b the rows s < len_b (len_b = 1 + its last un-masked
- * position in the host mask) are one strided 2-D copy; the padded tail is never read by any kernel.  (TNT_H2D_LIVE_ROWS=0
- * restores the full copy.)  tnt_decoder_last_h2d_bytes = bytes the last score_host / submit call actually copied. */
+ * position in the host mask) are one strided 2-D copy.  A source for which that does not pay (every strided copy costs the
+ * DMA engine ~3.5 us on top of its bytes: a source without padding, or a small one) crosses as ONE contiguous copy and its
+ * padded tails are cleared on the device.  Either way no kernel ever sees what the host tensor holds in a padded tail.
+ * (TNT_H2D_LIVE_ROWS=0 restores the full copy.)  tnt_decoder_last_h2d_bytes = bytes the last score_host / submit call
+ * actually copied. */
 uint64_t tnt_decoder_last_h2d_bytes(const tnt_decoder* d);
 
 /* The live-row copy on its own (for callers that prefetch their step inputs themselves): dst [S, B, E] device, src [S, B, E]
  * pinned host, mask_host [B, S] bytes (nonzero = padding; NULL = plain copy).  Returns the bytes copied (< 0: tnt_status).
- * Skipped rows of dst keep their previous contents: zero dst once. */
+ * Skipped rows of dst keep their previous contents: zero dst once.  When skipping the padding would not pay for the strided
+ * copies' fixed cost the whole tensor is copied in one piece instead (the padded rows of dst then hold what src holds). */
 int64_t tnt_h2d_live_rows(void* dst, const void* src_host, const uint8_t* mask_host, int S, int B, int E, int dtype,
                           tnt_stream stream);
 

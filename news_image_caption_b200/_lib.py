@@ -158,6 +158,8 @@ _SIGS = {
     'tnt_dynconv_bwd': (i32, [C.POINTER(DynconvBwdParams), vp]),
     'tnt_dynconv_step': (i32, [C.POINTER(DynconvStepParams), vp]),
     'tnt_layernorm_fwd': (i32, [C.POINTER(LayernormParams), vp]),
+    'tnt_linear_ln_supported': (i32, [C.POINTER(LinearParams), vp, vp]),
+    'tnt_linear_ln_fwd': (i32, [C.POINTER(LinearParams), vp, vp, i64, f32, i32, i32, vp]),
     'tnt_layernorm_bwd': (i32, [C.POINTER(LayernormBwdParams), vp]),
     'tnt_lse_fwd_static': (i32, [C.POINTER(LseParams), vp]),
     'tnt_lse_fwd_static_max_bytes': (C.c_size_t, []),
@@ -234,6 +236,7 @@ _SIGS = {
     'tnt_debug_gemm_single_acc': (None, [i32]),
     'tnt_debug_gemm_split_k': (None, [i32]),
     'tnt_debug_sub_batches': (None, [i32]),
+    'tnt_debug_ln_fused': (None, [i32]),
     'tnt_debug_kv_beside': (None, [i32]),
     'tnt_debug_kv_inline': (None, [i32]),
     'tnt_debug_kv_beside_get': (i32, []),

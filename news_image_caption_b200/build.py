@@ -7,7 +7,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 OUT = os.path.join(HERE, 'libtnt_b200.so')
-SOURCES = ['core.cu', 'gemm.cu', 'gemm_splitk.cu', 'dynconv.cu', 'elementwise.cu', 'context.cu', 'pointer.cu', 'backward.cu', 'attention.cu', 'attention_tc.cu', 'attention_step.cu', 'attention_short.cu', 'attention_bwd.cu', 'attention_bwd_tc.cu', 'adasoftmax.cu',
+SOURCES = ['core.cu', 'gemm.cu', 'gemm_splitk.cu', 'gemm_ln.cu', 'dynconv.cu', 'elementwise.cu', 'context.cu', 'pointer.cu', 'backward.cu', 'attention.cu', 'attention_tc.cu', 'attention_step.cu', 'attention_short.cu', 'attention_bwd.cu', 'attention_bwd_tc.cu', 'adasoftmax.cu',
            'engine_load.cu', 'engine_fwd.cu', 'engine_gen.cu', 'engine_beam.cu', 'engine_train.cu', 'optimizer.cu']
 FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
          '-Xcompiler', '-fPIC', '-DNDEBUG']

@@ -16,6 +16,10 @@ int xattn_live_order(const uint32_t* tile_live, int B, int* order, cudaStream_t 
 bool xattn_force_simt();
 bool xattn_short_supported(const tnt_xattn_params* p);
 int xattn_short_multi(const tnt_xattn_params* ps, int n, cudaStream_t st);
+bool linear_ln_enabled();                                                                                    // gemm_ln.cu
+bool linear_ln_supported(const tnt_linear_params* p, const float* gamma, const float* beta);
+int launch_linear_ln(const tnt_linear_params* p, const float* gamma, const float* beta, long stride_gb, float eps, int tT, int tB,
+                     cudaStream_t st);
 
 namespace {
 inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
@@ -41,6 +45,27 @@ int layernorm(const void* x, void* y, long ld, const float* g, const float* b, i
   p.rows = rows; p.C = C; p.groups = groups; p.variant = 0; p.eps = 1e-5f; p.dtype = dtype;
   p.transpose_T = tT; p.transpose_B = tB;
   return tnt_layernorm_fwd(&p, st);
+}
+// out = LayerNorm(a . w^T + bias + res): ONE launch (gemm_ln.cu: a cluster of CTAs per 128-row block, row statistics through
+// distributed shared memory) when `fuse` and the shape allows it, else the GEMM into `tmp` followed by the LayerNorm kernel.
+// Grouped form (per-source out_proj + context_attn_lns): group s reads a + s*sa / w + s*sw / bias + s*sb, writes columns
+// [s*sc, s*sc + N) of `out` and normalises them with gamma / beta block s.
+int linear_res_ln(const void* a, long lda, const void* w, long ldw, const float* bias, const void* res, long ldr, void* tmp, void* out,
+                  long ldo, int M, int N, int K, int dtype, const float* gamma, const float* beta, int groups, long sa, long sw,
+                  long sb, long sc, const void* pf, size_t pf_bytes, int tT, int tB, const tnt_dropout* drop, bool fuse,
+                  cudaStream_t st) {
+  if (fuse) {
+    tnt_linear_params p = {};
+    p.a = a; p.lda = lda; p.w = w; p.ldw = ldw; p.bias = bias; p.residual = res; p.ldr = ldr; p.c = out; p.ldc = ldo;
+    p.M = M; p.N = N; p.K = K; p.groups = groups;
+    p.stride_a = sa; p.stride_w = sw; p.stride_bias = sb; p.stride_res = 0; p.stride_c = sc;
+    p.dtype_in = dtype; p.dtype_out = dtype; p.epilogue = EPI_RESIDUAL;
+    p.prefetch = pf; p.prefetch_bytes = pf_bytes;
+    if (linear_ln_supported(&p, gamma, beta)) return launch_linear_ln(&p, gamma, beta, N, 1e-5f, tT, tB, st);
+  }
+  TNT_TRY(linear(a, lda, w, ldw, bias, tmp, ldo, M, N, K, dtype, EPI_RESIDUAL, res, ldr, st, groups, sa, sw, sb, 0, sc, pf, pf_bytes, drop));
+  // the grouped LayerNorm sees [M, groups * N] as M * groups rows of N (block = row % groups)
+  return layernorm(tmp, out, groups > 1 ? N : ldo, gamma, beta, M * groups, N, groups, dtype, tT, tB, st);
 }
 // rows S and S+1 of a K/V buffer: the learned bias_k|bias_v row and the all-zero row that
 // add_bias_kv / add_zero_attn append to every source (multi_head.py:355-374, 416-427)
@@ -370,8 +395,10 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
                                from_x * row, cudaMemcpyDeviceToDevice, st));
     }
   }
-  TNT_TRY(linear(w.cbuf, d, L.w2, d, L.b2, w.ybuf, d, N, d, d, dt, EPI_RESIDUAL, Xin, d, st, 1, 0, 0, 0, 0, 0, L.wq, ns * dd, &d_conv));
-  TNT_TRY(layernorm(w.ybuf, w.X1, d, L.ln_conv_g, L.ln_conv_b, N, d, 1, dt, 0, 0, st));
+  // LayerNorm folded into the producing GEMM (inference, bf16): the pre-LayerNorm tensors are not kept
+  const bool fuse_ln = !dr && dt == TNT_BF16 && w.ybuf2 == w.ybuf && w.CATln == w.CAT && linear_ln_enabled();
+  TNT_TRY(linear_res_ln(w.cbuf, d, L.w2, d, L.b2, Xin, d, w.ybuf, w.X1, d, N, d, d, dt, L.ln_conv_g, L.ln_conv_b, 1, 0, 0, 0, 0,
+                        L.wq, ns * dd, 0, 0, &d_conv, fuse_ln, st));
   // multi-source cross attention: one stacked query projection, per-source attention, grouped out-proj
   TNT_TRY(linear(w.X1, d, L.wq, d, L.bq, w.Q, static_cast<long>(ns) * d, N, ns * d, d, dt, EPI_NONE, nullptr, 0, st, 1, 0, 0, 0, 0, 0,
                  L.wo, ns * dd));
@@ -447,17 +474,24 @@ int run_layer(tnt_decoder* D, int l, const tnt_contexts* ctx, const FwdWs& w, co
       prof_end(pid, st);
     }
   }
-  TNT_TRY(linear(w.AO, static_cast<long>(ns) * d, L.wo, d, L.bo, w.CAT, static_cast<long>(ns) * d, N, d, d, dt, EPI_RESIDUAL,
-                 w.X1, d, st, ns, d, static_cast<long>(d) * d, d, 0, d, L.wc, ns * dd, &d_attn));
-  TNT_TRY(layernorm(w.CAT, w.CATln, d, L.ln_src_g, L.ln_src_b, N * ns, d, ns, dt, 0, 0, st));
+  if (fuse_ln) {
+    TNT_TRY(linear_res_ln(w.AO, static_cast<long>(ns) * d, L.wo, d, L.bo, w.X1, d, w.CAT, w.CATln, static_cast<long>(ns) * d, N, d, d,
+                          dt, L.ln_src_g, L.ln_src_b, ns, d, static_cast<long>(d) * d, d, d, L.wc, ns * dd, 0, 0, &d_attn, true, st));
+  } else {
+    TNT_TRY(linear(w.AO, static_cast<long>(ns) * d, L.wo, d, L.bo, w.CAT, static_cast<long>(ns) * d, N, d, d, dt, EPI_RESIDUAL,
+                   w.X1, d, st, ns, d, static_cast<long>(d) * d, d, 0, d, L.wc, ns * dd, &d_attn));
+    TNT_TRY(layernorm(w.CAT, w.CATln, d, L.ln_src_g, L.ln_src_b, N * ns, d, ns, dt, 0, 0, st));
+  }
   TNT_TRY(linear(w.CATln, static_cast<long>(ns) * d, L.wc, static_cast<long>(ns) * d, L.bc, w.X0, d, N, d, ns * d, dt, EPI_NONE,
                  nullptr, 0, st, 1, 0, 0, 0, 0, 0, L.wf1, static_cast<size_t>(c.ffn) * d * E));
   // feed-forward
   TNT_TRY(linear(w.X0, d, L.wf1, d, L.bf1, w.F, c.ffn, N, c.ffn, d, dt, EPI_RELU, nullptr, 0, st, 1, 0, 0, 0, 0, 0, L.wf2,
                  static_cast<size_t>(c.ffn) * d * E, &d_relu));
-  TNT_TRY(linear(w.F, c.ffn, L.wf2, c.ffn, L.bf2, w.ybuf2, d, N, d, c.ffn, dt, EPI_RESIDUAL, w.X0, d, st, 1, 0, 0, 0, 0, 0, next_w1,
-                 next_w1_bytes, &d_ffn));
-  TNT_TRY(layernorm(w.ybuf2, Xout, d, L.ln_f_g, L.ln_f_b, N, d, 1, dt, transpose_out ? T : 0, transpose_out ? B : 0, st));
+  // (fc2 has K = ffn = 4096: a cluster CTA owns a 128 x 256 tile and walks 64 k-blocks, 31 us at B*T = 2048 where the
+  // persistent GEMM's 128 narrower tiles + the LayerNorm kernel take 27 us; at a decode step's few rows the split-K form wins)
+  TNT_TRY(linear_res_ln(w.F, c.ffn, L.wf2, c.ffn, L.bf2, w.X0, d, w.ybuf2, Xout, d, N, d, c.ffn, dt, L.ln_f_g, L.ln_f_b, 1, 0, 0, 0, 0,
+                        next_w1, next_w1_bytes, transpose_out ? T : 0, transpose_out ? B : 0, &d_ffn,
+                        fuse_ln && c.ffn <= 2048, st));
   return TNT_OK;
 }
 

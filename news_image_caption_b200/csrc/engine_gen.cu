@@ -378,6 +378,26 @@ __global__ void __launch_bounds__(256) h2d_live_rows_kernel(uint4* dst, const ui
   }
 }
 
+// rows s >= len_b of caption b (len_b = 1 + its last un-masked position) of dst [S, B, row16 * 16 bytes] are cleared: the padded
+// tail of a source that crossed PCIe as ONE contiguous copy never reaches the kernels as whatever the host tensor held there
+__global__ void __launch_bounds__(256) zero_tail_rows_kernel(uint4* dst, const uint8_t* mask, int S, int B, int row16) {
+  __shared__ int s_len;
+  const int b = blockIdx.x;
+  if (threadIdx.x == 0) s_len = 0;
+  __syncthreads();
+  int last = 0;
+  for (int s = threadIdx.x; s < S; s += blockDim.x)
+    if (!mask[static_cast<size_t>(b) * S + s]) last = s + 1;
+  if (last) atomicMax(&s_len, last);
+  __syncthreads();
+  const int len = s_len;
+  const long n = static_cast<long>(S - len) * row16;
+  for (long i = threadIdx.x; i < n; i += blockDim.x) {
+    const long s = len + i / row16, c = i % row16;
+    dst[(s * B + b) * row16 + c] = make_uint4(0, 0, 0, 0);
+  }
+}
+
 // device-visible aliases of pinned host pointers (UVA: normally the same address); false = not mapped, use the DMA path
 bool host_dev_ptr(const void* host, const void** dev) {
   void* p = nullptr;
@@ -389,8 +409,9 @@ bool host_dev_ptr(const void* host, const void** dev) {
   return true;
 }
 
-int h2d_source(tnt_decoder* D, void* dst, const void* src_host, const uint8_t* mask_host, int S, int B, int E, size_t esz,
-               cudaStream_t st, size_t* bytes_out) {
+// mask_dev: the same mask already on the device, uploaded on `st` before this call (or NULL when mask_host is)
+int h2d_source(tnt_decoder* D, void* dst, const void* src_host, const uint8_t* mask_host, const uint8_t* mask_dev, int S, int B, int E,
+               size_t esz, cudaStream_t st, size_t* bytes_out) {
   const size_t row = static_cast<size_t>(E) * esz, all = static_cast<size_t>(S) * B * row;
   if (!all) return TNT_OK;
   static const bool live_only = [] { const char* e = getenv("TNT_H2D_LIVE_ROWS"); return !(e && e[0] == '0'); }();
@@ -418,18 +439,22 @@ int h2d_source(tnt_decoder* D, void* dst, const void* src_host, const uint8_t* m
       n_copies += len > 0;
     }
     const double t_all = static_cast<double>(all) / 40e9, t_live = static_cast<double>(live) / 40e9 + n_copies * 3.5e-6;
-    if (t_all <= t_live) {
+    if (t_all <= t_live && (live == all || (mask_dev && row % 16 == 0 && aligned16(dst)))) {
       TNT_CUDA(cudaMemcpyAsync(dst, src_host, all, cudaMemcpyHostToDevice, st));
       if (bytes_out) *bytes_out += all;
+      if (live < all) {       // the padded tails came along: cleared on the device, no kernel ever sees the host's contents
+        zero_tail_rows_kernel<<<B, 256, 0, st>>>(static_cast<uint4*>(dst), mask_dev, S, B, static_cast<int>(row / 16));
+        TNT_LAUNCHED();
+      }
       return TNT_OK;
     }
   }
   static const bool zero_copy = [] { const char* e = getenv("TNT_H2D_ZEROCOPY"); return e && e[0] == '1'; }();   // measured slower: off
-  const void *src_dev = nullptr, *mask_dev = nullptr;
+  const void *src_dev = nullptr, *mask_zc = nullptr;
   if (zero_copy && row % 16 == 0 && aligned16(dst) && aligned16(src_host) && host_dev_ptr(src_host, &src_dev) &&
-      host_dev_ptr(mask_host, &mask_dev)) {
+      host_dev_ptr(mask_host, &mask_zc)) {
     h2d_live_rows_kernel<<<std::min(B, 2 * num_sms()), 256, 0, st>>>(static_cast<uint4*>(dst), static_cast<const uint4*>(src_dev),
-                                                                     static_cast<const uint8_t*>(mask_dev), S, B,
+                                                                     static_cast<const uint8_t*>(mask_zc), S, B,
                                                                      static_cast<int>(row / 16));
     TNT_LAUNCHED();
     if (bytes_out) {
@@ -505,8 +530,6 @@ extern "C" int tnt_decoder_score_host(tnt_decoder* D, const int64_t* ids_host, c
   D->last_h2d_bytes = 2 * sizeof(int64_t) * B * T;
   tnt_contexts cd = *ch;
   for (int i = 0; i < D->cfg.n_sources; ++i) {
-    TNT_TRY(h2d_source(D, s.mem[i], ch->memory[i], ch->pad_mask[i], ch->S[i], B, D->cfg.source_dim[i], D->esz(), st, &D->last_h2d_bytes));
-    cd.memory[i] = s.mem[i];
     if (ch->pad_mask[i] && ch->S[i]) {
       TNT_CUDA(cudaMemcpyAsync(s.mask[i], ch->pad_mask[i], static_cast<size_t>(ch->S[i]) * B, cudaMemcpyHostToDevice, st));
       D->last_h2d_bytes += static_cast<size_t>(ch->S[i]) * B;
@@ -514,6 +537,9 @@ extern "C" int tnt_decoder_score_host(tnt_decoder* D, const int64_t* ids_host, c
     } else {
       cd.pad_mask[i] = nullptr;
     }
+    TNT_TRY(h2d_source(D, s.mem[i], ch->memory[i], ch->pad_mask[i], cd.pad_mask[i], ch->S[i], B, D->cfg.source_dim[i], D->esz(), st,
+                       &D->last_h2d_bytes));
+    cd.memory[i] = s.mem[i];
   }
   const size_t fwd = carve_fwd(D, B, T, ch->S, nullptr, true).total;
   const size_t loss = adasoftmax_workspace_bytes(D->ada, B * T, false);
@@ -557,8 +583,6 @@ extern "C" int tnt_decoder_score_host_submit(tnt_decoder* D, int slot, const int
   D->last_h2d_bytes = 2 * sizeof(int64_t) * B * T;
   tnt_contexts cd = *ch;
   for (int i = 0; i < D->cfg.n_sources; ++i) {
-    TNT_TRY(h2d_source(D, s.mem[i], ch->memory[i], ch->pad_mask[i], ch->S[i], B, D->cfg.source_dim[i], D->esz(), cs, &D->last_h2d_bytes));
-    cd.memory[i] = s.mem[i];
     if (ch->pad_mask[i] && ch->S[i]) {
       TNT_CUDA(cudaMemcpyAsync(s.mask[i], ch->pad_mask[i], static_cast<size_t>(ch->S[i]) * B, cudaMemcpyHostToDevice, cs));
       D->last_h2d_bytes += static_cast<size_t>(ch->S[i]) * B;
@@ -566,6 +590,9 @@ extern "C" int tnt_decoder_score_host_submit(tnt_decoder* D, int slot, const int
     } else {
       cd.pad_mask[i] = nullptr;
     }
+    TNT_TRY(h2d_source(D, s.mem[i], ch->memory[i], ch->pad_mask[i], cd.pad_mask[i], ch->S[i], B, D->cfg.source_dim[i], D->esz(), cs,
+                       &D->last_h2d_bytes));
+    cd.memory[i] = s.mem[i];
   }
   TNT_CUDA(cudaEventRecord(D->ev_h2d[slot], cs));
   TNT_CUDA(cudaStreamWaitEvent(st, D->ev_h2d[slot], 0));

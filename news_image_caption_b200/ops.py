@@ -90,6 +90,37 @@ def linear(a, w, bias=None, epilogue=EPI_NONE, residual=None, out_dtype=None, la
     return c
 
 
+def linear_ln(a, w, bias, residual, gamma, beta, eps=1e-5, groups=1, transpose_tb=None):
+    """LayerNorm(a @ w^T + bias + residual) * gamma + beta in one launch (tnt_linear_ln_fwd; bf16).
+    groups == 1: a [M, K], w [N, K], residual [M, N] or None, gamma / beta [N] -> [M, N].
+    groups > 1 (the per-source out_proj + context_attn_lns): a [M, groups * K], w [groups, N, K], bias / gamma / beta
+    [groups, N], residual [M, N] shared by the groups -> [M, groups * N], every N-wide block normalised on its own.
+    transpose_tb = (T, B): rows are in t*B + b order, the result is written as [B, T, N]."""
+    a, w = _cuda(a).contiguous(), _cuda(w).contiguous()
+    M = a.shape[0]
+    N, K = w.shape[-2], w.shape[-1]
+    out = torch.empty(M, groups * N, dtype=a.dtype, device=a.device) if transpose_tb is None else \
+        torch.empty(transpose_tb[1], transpose_tb[0], N, dtype=a.dtype, device=a.device)
+    p = _lib.LinearParams()
+    p.a, p.lda, p.w, p.ldw = a.data_ptr(), a.shape[1], w.data_ptr(), K
+    bias = bias.float().contiguous() if bias is not None else None
+    p.bias = bias.data_ptr() if bias is not None else None
+    if residual is not None:
+        residual = residual.contiguous()
+        p.residual, p.ldr = residual.data_ptr(), residual.shape[1]
+    p.c, p.ldc, p.M, p.N, p.K, p.groups = out.data_ptr(), groups * N, M, N, K, groups
+    p.stride_a, p.stride_w, p.stride_bias, p.stride_res, p.stride_c = (K, N * K, N, 0, N) if groups > 1 else (0, 0, 0, 0, 0)
+    p.dtype_in, p.dtype_out = _code(a), _code(out)
+    p.epilogue = EPI_RESIDUAL if residual is not None else EPI_NONE
+    gamma, beta = gamma.float().contiguous(), beta.float().contiguous()
+    L = _lib.lib()
+    if not L.tnt_linear_ln_supported(C.byref(p), gamma.data_ptr(), beta.data_ptr()):
+        raise RuntimeError('tnt_linear_ln_fwd: unsupported problem M=%d N=%d K=%d groups=%d %s' % (M, N, K, groups, a.dtype))
+    tT, tB = transpose_tb if transpose_tb is not None else (0, 0)
+    _lib.check(L.tnt_linear_ln_fwd(C.byref(p), gamma.data_ptr(), beta.data_ptr(), N, eps, tT, tB, _st()), 'tnt_linear_ln_fwd')
+    return out
+
+
 def wn_fold(v, g=None, glu_interleave=False, dtype=torch.float32):
     v = _cuda(v).float().contiguous()
     out = torch.empty(v.shape, dtype=dtype, device=v.device)

@@ -147,14 +147,16 @@ def test_out_of_range_token_id_is_loud():
 @pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
 def test_host_scoring_copies_live_rows_only(dtype):
     """tnt_decoder_score_host / _submit: ids, targets, contexts and masks in PINNED HOST memory.  Only the live rows of a
-    masked source cross PCIe (one strided 2-D copy per caption up to its last un-masked position); the result must equal
-    the device-resident forward + loss -- incl. a caption whose article is all padding, one without padding, masks with
-    holes, NaN in the padded tail of the host tensor (never copied), and a second batch reusing the staging buffer."""
+    masked source cross PCIe (one strided 2-D copy per caption up to its last un-masked position) when skipping the padding
+    pays for the copies' fixed cost (S_art = 300); a source too small for that (S_art = 37) crosses as one contiguous copy
+    and its padded tails are cleared on the device.  Either way the result must equal the device-resident forward + loss --
+    incl. a caption whose article is all padding, one without padding, masks with holes, NaN in the padded tail of the host
+    tensor (never seen by a kernel), and a second batch reusing the staging buffer."""
     from news_image_caption_b200 import _lib
     dec, sd = make(dtype)
     pin = lambda t: t.contiguous().pin_memory()
-    for seed, poison in ((61, True), (67, False)):
-        prev, tgt, ctx = synth.make_batch(5, 6, V, seed=seed, S_img=4, S_art=37)
+    for seed, poison, S_art in ((61, True, 37), (67, False, 37), (71, True, 300), (73, False, 300)):
+        prev, tgt, ctx = synth.make_batch(5, 6, V, seed=seed, S_img=4, S_art=S_art)
         ctx['article_mask'][0] = True                     # nothing live
         ctx['article_mask'][1] = False                    # everything live
         ctx['article_mask'][2, 3:9] = True                # a hole inside the live prefix (those rows are copied, masked later)
@@ -162,7 +164,7 @@ def test_host_scoring_copies_live_rows_only(dtype):
         X, _ = dec(prev.cuda(), cc)
         want = dec.nll(X, tgt.cuda()).cpu()
         host = {k: pin(v.to(dec.torch_dtype) if v.is_floating_point() else v) for k, v in ctx.items()}
-        if poison:                                        # the padded TAIL of every caption is never read
+        if poison:                                        # the padded TAIL of every caption never reaches a kernel
             m = ctx['article_mask']
             for b in range(5):
                 live = (~m[b]).nonzero()
@@ -172,7 +174,7 @@ def test_host_scoring_copies_live_rows_only(dtype):
         assert n_tok == want[1].item() and abs(l - want[0].item()) < 1e-5 * abs(want[0].item())
         full = sum(v.numel() * v.element_size() for v in host.values()) + 2 * prev.numel() * 8
         sent = _lib.lib().tnt_decoder_last_h2d_bytes(dec._h())
-        assert sent < full                                 # fewer bytes than the padded tensors hold
+        assert sent < full if S_art == 300 else sent <= full     # fewer bytes than the padded tensors hold
         dec.score_host_submit(0, pin(prev), pin(tgt), host)
         l2, n2 = dec.score_host_wait(0)
         assert n2 == n_tok and abs(l2 - l) < 1e-6 * abs(l)

@@ -324,6 +324,59 @@ def test_layernorm(ops):
     assert rel_err(dx, gx) < 1e-4 and rel_err(dg, gg) < 1e-4 and rel_err(db, gb) < 1e-4
 
 
+# ----------------------------------------------------------------------------- Linear + residual + LayerNorm, one launch
+@pytest.mark.parametrize('M,N,K,groups', [(2048, 1024, 1024, 1),      # a layer site at the bench's B*T: 16 clusters of 8 CTAs
+                                          (300, 1024, 4096, 1),       # ragged last block, long K (fc2)
+                                          (2048, 1024, 1024, 2),      # per-source out_proj + context_attn_lns: 4 CTAs x 256 columns
+                                          (256, 1024, 1024, 4),       # decode-step rows, four sources
+                                          (100, 512, 1024, 1),        # 8 CTAs x 64 columns
+                                          (130, 2048, 512, 1)])       # 8 CTAs x 256 columns
+def test_linear_residual_layernorm_fused(ops, M, N, K, groups):
+    """tnt_linear_ln_fwd (gemm_ln.cu: a cluster of CTAs per 128-row block, row statistics through distributed shared memory)
+    against fp32 torch on the bf16-rounded operands, and against the two-launch form it replaces (tnt_linear_fwd with the
+    residual epilogue, then tnt_layernorm_fwd).  bf16 outputs: 2e-2 of the largest value; against the two-launch form the
+    only difference is that the fused kernel does not round the pre-LayerNorm row to bf16."""
+    g = torch.Generator().manual_seed(11)
+    a = torch.randn(M, groups * K, generator=g).bfloat16()
+    w = (torch.randn(groups, N, K, generator=g) / K ** 0.5).bfloat16()
+    bias = torch.randn(groups, N, generator=g)
+    res = (torch.randn(M, N, generator=g) * 2 + 0.5).bfloat16()
+    gm, bt = torch.rand(groups, N, generator=g) + 0.5, torch.randn(groups, N, generator=g)
+    ref = torch.cat([F.layer_norm(a[:, s * K:(s + 1) * K].float() @ w[s].float().t() + bias[s] + res.float(), (N,), gm[s], bt[s])
+                     for s in range(groups)], 1)
+    if groups == 1:
+        y = ops.linear_ln(a.cuda(), w[0].cuda(), bias[0].cuda(), res.cuda(), gm[0].cuda(), bt[0].cuda())
+    else:
+        y = ops.linear_ln(a.cuda(), w.cuda(), bias.cuda(), res.cuda(), gm.cuda(), bt.cuda(), groups=groups)
+    assert y.shape == (M, groups * N)
+    assert rel_err(y, ref) < 2e-2
+    two = torch.cat([ops.layernorm(ops.linear(a[:, s * K:(s + 1) * K].cuda(), w[s].cuda(), bias[s].cuda(), epilogue=3, residual=res.cuda()),
+                                   gm[s].cuda(), bt[s].cuda()) for s in range(groups)], 1)
+    assert rel_err(y, two) < 2e-2
+    # tighter, on the error mass: both forms agree with the fp32 result to bf16 rounding, the fused one at least as well
+    e_f = (y.float().cpu() - ref).norm() / ref.norm()
+    e_t = (two.float().cpu() - ref).norm() / ref.norm()
+    assert e_f < 4e-3 and e_f < 1.2 * e_t + 1e-4, (e_f, e_t)
+
+
+def test_linear_residual_layernorm_fused_transposed_store_and_no_residual(ops):
+    """the last layer's site writes batch-major rows: row t*B + b of the problem lands in row b*T + t of the output."""
+    g = torch.Generator().manual_seed(12)
+    T, B, N, K = 32, 5, 1024, 1024
+    a = torch.randn(T * B, K, generator=g).bfloat16()
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).bfloat16()
+    bias, gm, bt = torch.randn(N, generator=g), torch.rand(N, generator=g) + 0.5, torch.randn(N, generator=g)
+    res = torch.randn(T * B, N, generator=g).bfloat16()
+    ref = F.layer_norm(a.float() @ w.float().t() + bias + res.float(), (N,), gm, bt)
+    y = ops.linear_ln(a.cuda(), w.cuda(), bias.cuda(), res.cuda(), gm.cuda(), bt.cuda(), transpose_tb=(T, B))
+    assert y.shape == (B, T, N)
+    assert rel_err(y, ref.view(T, B, N).transpose(0, 1)) < 2e-2
+    ref0 = F.layer_norm(a.float() @ w.float().t(), (N,), gm, bt)
+    assert rel_err(ops.linear_ln(a.cuda(), w.cuda(), None, None, gm.cuda(), bt.cuda()), ref0) < 2e-2
+    with pytest.raises(RuntimeError):                       # fp32 operands: not a tcgen05 problem, the caller keeps two launches
+        ops.linear_ln(a.float().cuda(), w.float().cuda(), bias.cuda(), res.float().cuda(), gm.cuda(), bt.cuda())
+
+
 # ----------------------------------------------------------------------------- attention
 @pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
 def test_xattn_golden(ops, dtype):
