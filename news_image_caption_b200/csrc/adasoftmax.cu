@@ -34,6 +34,33 @@ __global__ void __launch_bounds__(256) lse_finish_kernel(const float4* partials,
   if (lane == 0) stats[row_map ? row_map[row] : row] = make_float4(a.m, a.s, __int_as_float(a.arg), a.tz);
 }
 
+// the same merge for SEVERAL clusters in one launch (blockIdx.y = cluster): loss / greedy calls run the clusters' GEMMs back to
+// back into per-cluster partial buffers and finish them together (two launches less per call)
+struct FinishJob { const float4* partials; int n_tiles; int M; const int* m_dyn; const int* row_map; float4* stats; };
+struct FinishJobs { FinishJob j[TNT_MAX_CLUSTERS]; int n; };
+__global__ void __launch_bounds__(256) lse_finish_multi_kernel(FinishJobs jobs) {
+  pdl_wait();
+  const FinishJob& J = jobs.j[blockIdx.y];
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int Me = J.m_dyn ? min(J.M, *J.m_dyn) : J.M;
+  if (row >= Me) return;
+  LseAcc a;
+  a.init();
+  for (int t = lane; t < J.n_tiles; t += 32) {
+    const float4 p = J.partials[static_cast<long>(row) * J.n_tiles + t];
+    a.merge(p.x, p.y, __float_as_int(p.z), p.w);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float m2 = __shfl_xor_sync(0xffffffffu, a.m, o), s2 = __shfl_xor_sync(0xffffffffu, a.s, o);
+    const float t2 = __shfl_xor_sync(0xffffffffu, a.tz, o);
+    const int a2 = __shfl_xor_sync(0xffffffffu, a.arg, o);
+    a.merge(m2, s2, a2, t2);
+  }
+  if (lane == 0) J.stats[J.row_map ? J.row_map[row] : row] = make_float4(a.m, a.s, __int_as_float(a.arg), a.tz);
+}
+
 // adapt_target (softmax.py:144-167): head targets + ordered per-tail row lists.  Single CTA -> the
 // row order inside each tail is the reference's (ascending), so results are run-to-run identical.
 __global__ void __launch_bounds__(1024) adapt_target_kernel(const int64_t* target, int N, AdaCuts c, int* head_t,
@@ -240,6 +267,34 @@ inline size_t al256(size_t x) { return (x + 255) & ~size_t(255); }
 
 }  // namespace
 
+static bool finish_merged() {     // TNT_LSE_FINISH_MERGED=0: one finish launch per cluster, as before
+  static const bool on = [] { const char* e = getenv("TNT_LSE_FINISH_MERGED"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
+static int lse_gemm_deferred(const void* x, long ldx, const void* w, long ldw, const float* bias, int M, int n_cols, int K, int dtype,
+                             const int* m_dyn, const int* target, const int* row_map, int n_lse, float* side, long side_ld,
+                             float4* partials, float4* stats, FinishJobs* jobs, cudaStream_t st) {
+  tnt_linear_params lp = {};
+  lp.a = x; lp.lda = ldx; lp.w = w; lp.ldw = ldw; lp.bias = bias;
+  lp.M = M; lp.N = n_cols; lp.K = K; lp.m_dyn = m_dyn; lp.groups = 1;
+  lp.dtype_in = dtype; lp.dtype_out = TNT_F32; lp.epilogue = EPI_LSE;
+  LseExtra ex = {target, partials, n_lse, side, side_ld};
+  int n_tiles = 0;
+  TNT_TRY(launch_gemm(&lp, EPI_LSE, &ex, &n_tiles, st));
+  jobs->j[jobs->n++] = FinishJob{partials, n_tiles, M, m_dyn, row_map, stats};
+  return TNT_OK;
+}
+
+static int lse_finish_jobs(const FinishJobs& jobs, cudaStream_t st) {
+  if (!jobs.n) return TNT_OK;
+  int maxM = 0;
+  for (int i = 0; i < jobs.n; ++i) maxM = std::max(maxM, jobs.j[i].M);
+  TNT_CUDA(launch_pdl(lse_finish_multi_kernel, dim3((maxM + 7) / 8, jobs.n), dim3(256), 0, st, 1, jobs));
+  TNT_LAUNCHED();
+  return TNT_OK;
+}
+
 int lse_gemm(const void* x, long ldx, const void* w, long ldw, const float* bias, int M, int n_cols, int K, int dtype,
              const int* m_dyn, const int* target, const int* row_map, int n_lse, float* side, long side_ld,
              float4* partials, float4* stats, cudaStream_t st) {
@@ -261,6 +316,7 @@ size_t lse_partials_bytes(int M, int n_cols) { return al256(static_cast<size_t>(
 struct AdaWs {
   int* head_t; int* tail_rows; int* tail_loc; int* counts;
   float4* head_stats; float* side; float4* tail_stats; float4* partials;
+  float4* partials_c[TNT_MAX_CLUSTERS];     // per cluster (0 = head, 1.. = tails): the merged finish reads them after the last GEMM
   void* xc; void* proj; float* head_raw;
   size_t total;
 };
@@ -284,6 +340,10 @@ static AdaWs carve(const AdaSoftmax& a, int N, void* ws, bool need_raw) {
   w.side = static_cast<float*>(take(sizeof(float) * N * std::max(nt, 1)));
   w.tail_stats = static_cast<float4*>(take(sizeof(float4) * N * std::max(nt, 1)));
   w.partials = static_cast<float4*>(take(lse_partials_bytes(N, max_cols)));
+  for (int i = 0; i < TNT_MAX_CLUSTERS; ++i) w.partials_c[i] = nullptr;
+  w.partials_c[0] = static_cast<float4*>(take(lse_partials_bytes(N, a.cuts.cut[0] + nt)));
+  for (int i = 0; i < nt && i + 1 < TNT_MAX_CLUSTERS; ++i)
+    w.partials_c[i + 1] = static_cast<float4*>(take(lse_partials_bytes(N, a.cuts.cut[i + 1] - a.cuts.cut[i])));
   w.xc = take(dtype_size(a.dtype) * N * a.d);
   w.proj = take(dtype_size(a.dtype) * N * a.d);
   w.head_raw = need_raw ? static_cast<float*>(take(sizeof(float) * N * (a.cuts.cut[0] + nt))) : nullptr;
@@ -312,8 +372,14 @@ int adasoftmax_nll(const AdaSoftmax& a, const void* x, long ldx, const int64_t* 
   const int nt = a.cuts.n - 1;
   adapt_target_kernel<<<1, 1024, 0, st>>>(target, N, a.cuts, w.head_t, w.tail_rows, w.tail_loc, w.counts);
   TNT_LAUNCHED();
-  TNT_TRY(lse_gemm(x, ldx, a.head_w, a.d, nullptr, N, a.cuts.cut[0] + nt, a.d, a.dtype, nullptr, w.head_t, nullptr,
-                   a.cuts.cut[0], w.side, nt, w.partials, w.head_stats, st));
+  const bool merged = finish_merged() && nt + 1 <= TNT_MAX_CLUSTERS;
+  FinishJobs jobs = {};
+  if (merged)
+    TNT_TRY(lse_gemm_deferred(x, ldx, a.head_w, a.d, nullptr, N, a.cuts.cut[0] + nt, a.d, a.dtype, nullptr, w.head_t, nullptr,
+                              a.cuts.cut[0], w.side, nt, w.partials_c[0], w.head_stats, &jobs, st));
+  else
+    TNT_TRY(lse_gemm(x, ldx, a.head_w, a.d, nullptr, N, a.cuts.cut[0] + nt, a.d, a.dtype, nullptr, w.head_t, nullptr,
+                     a.cuts.cut[0], w.side, nt, w.partials, w.head_stats, st));
   for (int i = 0; i < nt; ++i) {
     const int grid = std::min((N + 7) / 8, 4 * num_sms());
     if (a.dtype == TNT_BF16)
@@ -327,10 +393,16 @@ int adasoftmax_nll(const AdaSoftmax& a, const void* x, long ldx, const int64_t* 
     const bool fold = a.use_fold && a.fold_w[i];
     if (!fold) TNT_TRY(tail_proj(a, i, w.xc, a.d, N, w.counts + i, w.proj, st));
     const int ncols = a.cuts.cut[i + 1] - a.cuts.cut[i];
-    TNT_TRY(lse_gemm(fold ? w.xc : w.proj, a.d, fold ? a.fold_w[i] : a.out_w[i], a.d, nullptr, N, ncols, a.d, a.dtype, w.counts + i,
-                     w.tail_loc + static_cast<long>(i) * N, nullptr, ncols, nullptr, 0, w.partials,
-                     w.tail_stats + static_cast<long>(i) * N, st));
+    if (merged)
+      TNT_TRY(lse_gemm_deferred(fold ? w.xc : w.proj, a.d, fold ? a.fold_w[i] : a.out_w[i], a.d, nullptr, N, ncols, a.d, a.dtype,
+                                w.counts + i, w.tail_loc + static_cast<long>(i) * N, nullptr, ncols, nullptr, 0, w.partials_c[i + 1],
+                                w.tail_stats + static_cast<long>(i) * N, &jobs, st));
+    else
+      TNT_TRY(lse_gemm(fold ? w.xc : w.proj, a.d, fold ? a.fold_w[i] : a.out_w[i], a.d, nullptr, N, ncols, a.d, a.dtype, w.counts + i,
+                       w.tail_loc + static_cast<long>(i) * N, nullptr, ncols, nullptr, 0, w.partials,
+                       w.tail_stats + static_cast<long>(i) * N, st));
   }
+  TNT_TRY(lse_finish_jobs(jobs, st));
   nll_reduce_kernel<<<1, 1024, 0, st>>>(target, w.head_t, N, a.cuts, pad, w.head_stats, w.side, w.tail_stats, w.tail_loc,
                                         w.counts, out2);
   TNT_LAUNCHED();
@@ -355,15 +427,27 @@ int adasoftmax_greedy(const AdaSoftmax& a, const void* x, long ldx, int N, int64
     return TNT_ERR_WORKSPACE;
   }
   const int nt = a.cuts.n - 1;
-  TNT_TRY(lse_gemm(x, ldx, a.head_w, a.d, nullptr, N, a.cuts.cut[0] + nt, a.d, a.dtype, nullptr, nullptr, nullptr,
-                   a.cuts.cut[0], w.side, nt, w.partials, w.head_stats, st));
+  const bool merged = finish_merged() && nt + 1 <= TNT_MAX_CLUSTERS;
+  FinishJobs jobs = {};
+  if (merged)
+    TNT_TRY(lse_gemm_deferred(x, ldx, a.head_w, a.d, nullptr, N, a.cuts.cut[0] + nt, a.d, a.dtype, nullptr, nullptr, nullptr,
+                              a.cuts.cut[0], w.side, nt, w.partials_c[0], w.head_stats, &jobs, st));
+  else
+    TNT_TRY(lse_gemm(x, ldx, a.head_w, a.d, nullptr, N, a.cuts.cut[0] + nt, a.d, a.dtype, nullptr, nullptr, nullptr,
+                     a.cuts.cut[0], w.side, nt, w.partials, w.head_stats, st));
   for (int i = 0; i < nt; ++i) {
     const bool fold = a.use_fold && a.fold_w[i];
     if (!fold) TNT_TRY(tail_proj(a, i, x, ldx, N, nullptr, w.proj, st));
     const int ncols = a.cuts.cut[i + 1] - a.cuts.cut[i];
-    TNT_TRY(lse_gemm(fold ? x : w.proj, fold ? ldx : a.d, fold ? a.fold_w[i] : a.out_w[i], a.d, nullptr, N, ncols, a.d, a.dtype,
-                     nullptr, nullptr, nullptr, ncols, nullptr, 0, w.partials, w.tail_stats + static_cast<long>(i) * N, st));
+    if (merged)
+      TNT_TRY(lse_gemm_deferred(fold ? x : w.proj, fold ? ldx : a.d, fold ? a.fold_w[i] : a.out_w[i], a.d, nullptr, N, ncols, a.d,
+                                a.dtype, nullptr, nullptr, nullptr, ncols, nullptr, 0, w.partials_c[i + 1],
+                                w.tail_stats + static_cast<long>(i) * N, &jobs, st));
+    else
+      TNT_TRY(lse_gemm(fold ? x : w.proj, fold ? ldx : a.d, fold ? a.fold_w[i] : a.out_w[i], a.d, nullptr, N, ncols, a.d, a.dtype,
+                       nullptr, nullptr, nullptr, ncols, nullptr, 0, w.partials, w.tail_stats + static_cast<long>(i) * N, st));
   }
+  TNT_TRY(lse_finish_jobs(jobs, st));
   greedy_pick_kernel<<<(N + 255) / 256, 256, 0, st>>>(N, a.cuts, w.head_stats, w.side, w.tail_stats, tok, logp);
   TNT_LAUNCHED();
   return TNT_OK;
