@@ -108,3 +108,48 @@ def test_round2_struct_layouts():
                  'tnt_grad_accumulate', 'tnt_variant_count', 'tnt_decoder_error_flags', 'tnt_cast_background'):
         assert hasattr(L, name)
     assert L.tnt_variant_count(b'gemm.tc.pair') == 0 and L.tnt_variant_count(b'no.such.variant') == -1
+
+
+def test_linear_ln_support_rule_is_host_logic():
+    """tnt_linear_ln_supported (gemm_ln.cu): which GEMM -> +residual -> LayerNorm sites get the one-launch cluster kernel is
+    decided on the host from the parameter block alone (no launch, no GPU needed: the cluster-occupancy query falls back to an
+    estimate): bf16 NT problems whose row is C <= 8 tiles of 64 / 128 / 256 columns, no dropout, no device row count."""
+    import ctypes as C
+    from news_image_caption_b200 import _lib
+    L = _lib.lib()
+    for name in ('tnt_linear_ln_fwd', 'tnt_linear_ln_supported', 'tnt_debug_ln_fused', 'tnt_debug_ln_tile_n', 'tnt_debug_kv_beside',
+                 'tnt_debug_kv_beside_get', 'tnt_debug_kv_inline'):
+        assert hasattr(L, name)
+    assert L.tnt_variant_count(b'gemm.ln_fused') == 0 and L.tnt_variant_count(b'kv.beside') == 0
+    buf = (C.c_char * 4096)()
+    base = (C.addressof(buf) + 255) & ~255             # a 256-byte aligned fake address: only alignment is looked at
+
+    def params(M=2048, N=1024, K=1024, dtype=_lib.TNT_BF16, epilogue=_lib.EPI_RESIDUAL, groups=1, **kw):
+        p = _lib.LinearParams()
+        p.a = p.w = p.c = p.residual = base
+        p.lda, p.ldw, p.ldc, p.ldr = groups * K, K, groups * N, N
+        p.M, p.N, p.K, p.groups = M, N, K, groups
+        if groups > 1:
+            p.stride_a, p.stride_w, p.stride_bias, p.stride_c = K, N * K, N, N
+        p.dtype_in = p.dtype_out = dtype
+        p.epilogue = epilogue
+        for k, v in kw.items():
+            setattr(p, k, v)
+        return p
+    ok = lambda p: bool(L.tnt_linear_ln_supported(C.byref(p), base, base))
+    assert ok(params())                                                  # a layer site at B*T = 2048
+    assert ok(params(M=256, groups=2)) and ok(params(M=100, N=512)) and ok(params(M=130, N=2048, K=512))
+    assert ok(params(epilogue=_lib.EPI_NONE))
+    assert not ok(params(dtype=_lib.TNT_F32))                            # not a tcgen05 problem
+    assert not ok(params(N=1000)) and not ok(params(N=4096))             # not C <= 8 tiles of 64 / 128 / 256 columns
+    assert not ok(params(epilogue=_lib.EPI_RELU))
+    assert not ok(params(layout=1))                                      # NN / TN operands
+    assert not ok(params(m_dyn=base))                                    # device-side row count
+    assert not ok(params(ldc=1028))                                      # rows without 16-byte alignment
+    pd = params()
+    pd.drop.p = 0.1                                                      # training dropout: two launches
+    assert not ok(pd)
+    pa = params()
+    pa.residual = base + 2
+    assert not ok(pa)
+    assert not L.tnt_linear_ln_supported(C.byref(params()), None, base)  # gamma missing
