@@ -153,3 +153,24 @@ def test_linear_ln_support_rule_is_host_logic():
     pa.residual = base + 2
     assert not ok(pa)
     assert not L.tnt_linear_ln_supported(C.byref(params()), None, base)  # gamma missing
+
+
+def test_bench_roofline_arithmetic():
+    """bench.py kv_roofline: achieved = algorithmic FLOPs of ONE launch / that launch's mean duration.  The forward issues the
+    article K/V projection once for all layers (N = L * 2d); with the per-layer schedules (TNT_KV_BESIDE_SMS / TNT_KV_INLINE)
+    it is four launches of a quarter of the columns -- the FLOPs per launch must follow, share_of_step must count all four."""
+    import bench
+    hbm, tf_burst, tf_sus, which = bench.peaks()
+    clocks = {'sm_mhz': 1965, 'sm_max_mhz': 1965}
+    one = bench.kv_roofline(64, {'prof': {'kv_proj.article': (20 * 0.4, 20)}, 'clocks': clocks, 'steps': 20}, 1.5)
+    assert one['shape'] == [512 * 64, 8192, 1024] and one['launches_timed'] == 20
+    assert abs(one['achieved'] - 2.0 * 512 * 64 * 8192 * 1024 / 0.4e-3 / 1e12) < 1e-6
+    assert abs(one['frac'] - one['achieved'] / tf_burst) < 1e-9 and abs(one['share_of_step'] - 0.4 / 1.5) < 1e-9
+    assert 'sm_share' not in one
+    four = bench.kv_roofline(64, {'prof': {'kv_proj.article': (80 * 0.15, 80)}, 'clocks': clocks, 'steps': 20}, 1.5)
+    assert four['shape'] == [512 * 64, 2048, 1024]
+    assert abs(four['achieved'] - 2.0 * 512 * 64 * 2048 * 1024 / 0.15e-3 / 1e12) < 1e-6
+    assert abs(four['share_of_step'] - 4 * 0.15 / 1.5) < 1e-9
+    # a part that settled well below its maximum clock is compared with the sustained peak
+    slow = bench.kv_roofline(64, {'prof': {'kv_proj.article': (20 * 0.5, 20)}, 'clocks': {'sm_mhz': 1300, 'sm_max_mhz': 1965}, 'steps': 20}, 1.5)
+    assert abs(slow['peak'] - tf_sus) < 1e-9
